@@ -1,0 +1,192 @@
+/* stan_cuda.h -- the C ABI of libstanmath_cuda.so (B200 / sm_100a).
+ *
+ * This is the drop-in boundary of the stan/math/cuda/ subsystem: plain C, plain pointers and
+ * sizes, no Eigen / Stan / torch types.  The C++ host layer (stan/math/cuda/*.hpp) binds these
+ * entry points from inside the reference's own function signatures; tests and bench.py bind
+ * them through ctypes.  No exception crosses this boundary.
+ *
+ * What each entry point replaces in the reference (paths relative to the Stan Math 3.0.0 tree):
+ *
+ *   stan_cuda_glm_eval           the numeric body of
+ *                                  bernoulli_logit_glm_lpmf  stan/math/prim/mat/prob/bernoulli_logit_glm_lpmf.hpp:80-135
+ *                                  poisson_log_glm_lpmf      stan/math/prim/mat/prob/poisson_log_glm_lpmf.hpp:82-129
+ *                                  normal_id_glm_lpdf        stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:89-172
+ *                                and the OpenCL overloads + kernels that did the same on matrix_cl
+ *                                  stan/math/opencl/prim/{bernoulli_logit,poisson_log,normal_id}_glm_*.hpp
+ *                                  stan/math/opencl/kernels/{bernoulli_logit,poisson_log,normal_id}_glm_*.hpp
+ *                                  stan/math/opencl/kernels/matrix_multiply.hpp:354-386 (row_vector_matrix_multiply)
+ *   stan_cuda_normal_lpdf_eval   the loop of normal_lpdf      stan/math/prim/scal/prob/normal_lpdf.hpp:67-110
+ *   stan_cuda_data_* / cache_*   matrix_cl + to_matrix_cl      stan/math/opencl/matrix_cl.hpp:32-454, stan/math/opencl/copy.hpp:37-93
+ *                                and the cache-by-call_id of the MPI backend
+ *                                  stan/math/prim/mat/functor/mpi_parallel_call.hpp:40-89
+ *   stan_cuda_init / describe    opencl_context               stan/math/opencl/opencl_context.hpp:54-383
+ *   stan_cuda_shard_scope_*      the per-job loop of map_rect_concurrent
+ *                                  stan/math/rev/mat/functor/map_rect_concurrent.hpp:39-54
+ *   stan_cuda_comm_*             (no counterpart: the reference is single-device; the closest is
+ *                                  the Boost.MPI cluster, stan/math/prim/arr/functor/mpi_cluster.hpp:126-241)
+ *
+ * Return convention (every int-returning function):
+ *    0  STAN_CUDA_OK
+ *    1  STAN_CUDA_NONFINITE   the evaluation ran but its result is not finite; outputs are written;
+ *                             the C++ wrapper then runs the reference's lazy check_finite sequence so
+ *                             the same std::domain_error is thrown (bernoulli_logit_glm_lpmf.hpp:106-110)
+ *   <0  failure (bad argument, CUDA or NCCL error); stan_cuda_last_error() has the text;
+ *       the C++ wrapper throws std::system_error (cf. stan/math/opencl/err/check_opencl.hpp)
+ *
+ * Threading: every function is re-entrant.  Each host thread gets its own stream, pinned staging
+ * and device scratch per device; the data cache is guarded by a mutex.  Results are deterministic:
+ * all reductions run in a fixed order, no floating-point atomics.
+ */
+#ifndef STAN_MATH_CUDA_C_API_H
+#define STAN_MATH_CUDA_C_API_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STAN_CUDA_OK 0
+#define STAN_CUDA_NONFINITE 1
+#define STAN_CUDA_ERR_ARG (-1)
+#define STAN_CUDA_ERR_CUDA (-2)
+#define STAN_CUDA_ERR_NCCL (-3)
+#define STAN_CUDA_ERR_STATE (-4)
+
+/* GLM families */
+#define STAN_CUDA_BERNOULLI_LOGIT 0
+#define STAN_CUDA_POISSON_LOG 1
+#define STAN_CUDA_NORMAL_ID 2
+
+/* flags: which summands of the log-density to include (the reference decides this at compile
+ * time with include_summand<propto, ...>, stan/math/prim/scal/meta/include_summand.hpp) and
+ * which partials the caller's operands_and_partials edges need. */
+#define STAN_CUDA_LP_CONST 0x01u   /* data-only terms: -sum lgamma(y+1) | N*NEG_LOG_SQRT_TWO_PI   */
+#define STAN_CUDA_LP_SCALE 0x02u   /* -sum log(sigma)  (normal_id_glm, normal_lpdf)                */
+#define STAN_CUDA_LP_MAIN 0x04u    /* the parameter-dependent part                                */
+#define STAN_CUDA_LP_ALL 0x07u
+#define STAN_CUDA_NEED_DBETA 0x08u
+#define STAN_CUDA_NEED_DALPHA 0x10u /* GLM: d/dalpha ; normal_lpdf: d/dmu                          */
+#define STAN_CUDA_NEED_DSIGMA 0x20u
+#define STAN_CUDA_NEED_DY 0x40u
+#define STAN_CUDA_NEED_ALL 0x78u
+
+typedef struct stan_cuda_glm_args {
+  int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID */
+  uint32_t flags;      /* STAN_CUDA_LP_* | STAN_CUDA_NEED_* */
+  int64_t n;           /* rows of x (instances) */
+  int64_t k;           /* columns of x (attributes) */
+  const double* x;     /* host, borrowed; cached on the device the first time it is seen */
+  int64_t ldx;         /* leading dimension in elements: >= n if column-major, >= k if row-major */
+  int32_t x_row_major; /* 0 = column-major (Eigen::MatrixXd), 1 = row-major */
+  int32_t y_is_double; /* 0: y is int32[n] (bernoulli, poisson); 1: y is double[n] */
+  const void* y;       /* host, borrowed; cached with x */
+  const double* alpha; /* host; alpha_len doubles */
+  int64_t alpha_len;   /* 1 (scalar intercept) or n */
+  const double* beta;  /* host; k doubles */
+  const double* sigma; /* host; normal_id only */
+  int64_t sigma_len;   /* 0 (not normal_id), 1 or n */
+  /* outputs: host memory owned by the caller, NULL when the matching NEED_ flag is off */
+  double* lp;          /* [1] */
+  double* dbeta;       /* [k] */
+  double* dalpha;      /* [alpha_len] */
+  double* dsigma;      /* [sigma_len] */
+  double* dy;          /* [n], normal_id only */
+  double* aux;         /* optional [4]: sum d, sum s^2, sum log sigma, sum lgamma(y+1) */
+} stan_cuda_glm_args;
+
+typedef struct stan_cuda_normal_args {
+  uint32_t flags;      /* STAN_CUDA_LP_* | NEED_DALPHA (= d/dmu) | NEED_DSIGMA | NEED_DY */
+  int32_t y_is_data;   /* 1: y is immutable data, cached on the device; 0: uploaded every call */
+  int64_t n;           /* max_size(y, mu, sigma) */
+  const double* y;
+  int64_t y_len;       /* 1 or n */
+  const double* mu;
+  int64_t mu_len;      /* 1 or n */
+  const double* sigma;
+  int64_t sigma_len;   /* 1 or n */
+  double* lp;          /* [1] */
+  double* dmu;         /* [mu_len] */
+  double* dsigma;      /* [sigma_len] */
+  double* dy;          /* [y_len] */
+} stan_cuda_normal_args;
+
+typedef struct stan_cuda_stats_t {
+  uint64_t cache_hits;
+  uint64_t cache_misses;
+  uint64_t bytes_uploaded;   /* cache-fill traffic, host -> device */
+  uint64_t evals;            /* GLM + normal_lpdf evaluations */
+  uint64_t kernel_launches;  /* launches of this library's own kernels */
+  uint64_t allreduces;       /* NCCL all-reduce calls */
+  double last_fill_ms;       /* wall time of the most recent cache fill */
+} stan_cuda_stats_t;
+
+/* ---- context -------------------------------------------------------------------------- */
+/* Use the first n_devices visible devices (0 = all; env STAN_CUDA_DEVICES overrides 0).
+ * Idempotent; implied by the first evaluation. */
+int stan_cuda_init(int n_devices);
+/* Bind this PROCESS to one device (one process per GPU: torchrun LOCAL_RANK). */
+int stan_cuda_init_device(int device_ordinal);
+int stan_cuda_device_count(void);
+/* Human-readable description of the devices in use (cf. opencl_context.description()). */
+const char* stan_cuda_describe(void);
+const char* stan_cuda_last_error(void); /* thread-local */
+int stan_cuda_stats(stan_cuda_stats_t* out);
+void stan_cuda_stats_reset(void);
+/* Rows are sharded over all devices of the process only when n*k reaches this many elements
+ * (default 1<<24); smaller problems stay on one device. */
+void stan_cuda_set_shard_min_elems(int64_t elems);
+
+/* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */
+int stan_cuda_glm_eval(const stan_cuda_glm_args* a);
+int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
+
+/* ---- data cache --------------------------------------------------------------------------- */
+int stan_cuda_cache_invalidate(const void* host_ptr); /* drop entries keyed on this x (or y) pointer */
+void stan_cuda_cache_clear(void);
+int64_t stan_cuda_cache_bytes(void);                  /* device bytes held by the cache */
+
+/* ---- map_rect shard scope (thread-local) ---------------------------------------------------- */
+/* Inside a scope, evaluations of the calling thread run on `device` and their data is keyed by
+ * (call_id, job) instead of by host pointer: the functor rebuilds X from x_r on every call, so
+ * its address is not an identity; the immutability contract is map_rect's own
+ * (stan/math/prim/mat/functor/map_rect.hpp:97-100). */
+void stan_cuda_shard_scope_enter(int call_id, int job, int device);
+void stan_cuda_shard_scope_exit(void);
+
+/* ---- multi-process communicator (one process per GPU) --------------------------------------- */
+/* Rank 0 creates the id; the host plumbing (torch.distributed, MPI, a file) carries the 128 bytes
+ * to every rank; every rank then calls comm_init_rank.  After that, sharded evaluations
+ * all-reduce [lp-parts, dbeta] across ranks with ncclAllReduce on the evaluation stream. */
+int stan_cuda_comm_unique_id(void* id128);
+int stan_cuda_comm_init_rank(int world_size, int rank, const void* id128);
+int stan_cuda_comm_world_size(void);
+void stan_cuda_comm_destroy(void);
+
+/* ---- device-level API (streams and buffers owned by the caller, e.g. torch) ---------------- */
+typedef struct stan_cuda_data* stan_cuda_data_t;
+
+/* Upload + re-layout of (x, y) of one GLM onto the current device: explicit cache fill. */
+int stan_cuda_data_create(int family, int64_t n, int64_t k, const double* x, int64_t ldx,
+                          int x_row_major, const void* y, int y_is_double, stan_cuda_data_t* out);
+void stan_cuda_data_destroy(stan_cuda_data_t d);
+/* Number of doubles of the parameter block / result block of a launch. */
+int64_t stan_cuda_data_params_len(stan_cuda_data_t d); /* = k_pad + 2: [beta(k_pad), alpha, sigma] */
+int64_t stan_cuda_data_result_len(stan_cuda_data_t d); /* = k_pad + 4: [lp, sum_d, sum_s2, status, dbeta(k_pad)] */
+int64_t stan_cuda_data_kpad(stan_cuda_data_t d);
+int64_t stan_cuda_data_algorithmic_bytes(stan_cuda_data_t d); /* n*k*8 + n*sizeof(y) */
+/* Enqueue one fused evaluation on `stream` (a cudaStream_t).  d_params / d_result are device
+ * pointers (layouts above); d_alpha_vec, d_sigma_vec, d_row_out may be NULL (scalar alpha/sigma,
+ * no per-row outputs).  No host synchronisation, no copies. */
+int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params,
+                         const double* d_alpha_vec, const double* d_sigma_vec, double* d_result,
+                         double* d_row_dalpha, double* d_row_dsigma, void* stream);
+/* All-reduce (sum) `count` doubles in place across the ranks of the communicator, on `stream`. */
+int stan_cuda_allreduce(double* d_buf, int64_t count, void* stream);
+/* Number of this library's kernels launched per stan_cuda_glm_launch call for this data. */
+int stan_cuda_data_launches_per_eval(stan_cuda_data_t d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STAN_MATH_CUDA_C_API_H */

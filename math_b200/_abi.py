@@ -1,0 +1,117 @@
+"""ctypes mirror of include/stan_cuda.h (structs, flags, prototypes).
+
+Pure declarations: importing this module loads nothing.  ``bind(lib)`` attaches the prototypes
+to a ``ctypes.CDLL`` of libstanmath_cuda.so; the test-side oracle loaders reuse the structs so
+that identical argument blocks can be handed to the CUDA library and to the CPU checkers.
+"""
+import ctypes as C
+
+OK, NONFINITE = 0, 1
+ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
+
+BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID = 0, 1, 2
+FAMILIES = {"bernoulli_logit": BERNOULLI_LOGIT, "poisson_log": POISSON_LOG, "normal_id": NORMAL_ID}
+
+LP_CONST, LP_SCALE, LP_MAIN, LP_ALL = 0x01, 0x02, 0x04, 0x07
+NEED_DBETA, NEED_DALPHA, NEED_DSIGMA, NEED_DY, NEED_ALL = 0x08, 0x10, 0x20, 0x40, 0x78
+
+c_double_p = C.POINTER(C.c_double)
+
+
+class GlmArgs(C.Structure):
+    _fields_ = [
+        ("family", C.c_int32),
+        ("flags", C.c_uint32),
+        ("n", C.c_int64),
+        ("k", C.c_int64),
+        ("x", C.c_void_p),
+        ("ldx", C.c_int64),
+        ("x_row_major", C.c_int32),
+        ("y_is_double", C.c_int32),
+        ("y", C.c_void_p),
+        ("alpha", C.c_void_p),
+        ("alpha_len", C.c_int64),
+        ("beta", C.c_void_p),
+        ("sigma", C.c_void_p),
+        ("sigma_len", C.c_int64),
+        ("lp", C.c_void_p),
+        ("dbeta", C.c_void_p),
+        ("dalpha", C.c_void_p),
+        ("dsigma", C.c_void_p),
+        ("dy", C.c_void_p),
+        ("aux", C.c_void_p),
+    ]
+
+
+class NormalArgs(C.Structure):
+    _fields_ = [
+        ("flags", C.c_uint32),
+        ("y_is_data", C.c_int32),
+        ("n", C.c_int64),
+        ("y", C.c_void_p),
+        ("y_len", C.c_int64),
+        ("mu", C.c_void_p),
+        ("mu_len", C.c_int64),
+        ("sigma", C.c_void_p),
+        ("sigma_len", C.c_int64),
+        ("lp", C.c_void_p),
+        ("dmu", C.c_void_p),
+        ("dsigma", C.c_void_p),
+        ("dy", C.c_void_p),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("cache_hits", C.c_uint64),
+        ("cache_misses", C.c_uint64),
+        ("bytes_uploaded", C.c_uint64),
+        ("evals", C.c_uint64),
+        ("kernel_launches", C.c_uint64),
+        ("allreduces", C.c_uint64),
+        ("last_fill_ms", C.c_double),
+    ]
+
+
+# name -> (restype, argtypes); exactly the symbols include/stan_cuda.h declares
+PROTOTYPES = {
+    "stan_cuda_init": (C.c_int, [C.c_int]),
+    "stan_cuda_init_device": (C.c_int, [C.c_int]),
+    "stan_cuda_device_count": (C.c_int, []),
+    "stan_cuda_describe": (C.c_char_p, []),
+    "stan_cuda_last_error": (C.c_char_p, []),
+    "stan_cuda_stats": (C.c_int, [C.POINTER(Stats)]),
+    "stan_cuda_stats_reset": (None, []),
+    "stan_cuda_set_shard_min_elems": (None, [C.c_int64]),
+    "stan_cuda_glm_eval": (C.c_int, [C.POINTER(GlmArgs)]),
+    "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
+    "stan_cuda_cache_invalidate": (C.c_int, [C.c_void_p]),
+    "stan_cuda_cache_clear": (None, []),
+    "stan_cuda_cache_bytes": (C.c_int64, []),
+    "stan_cuda_shard_scope_enter": (None, [C.c_int, C.c_int, C.c_int]),
+    "stan_cuda_shard_scope_exit": (None, []),
+    "stan_cuda_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "stan_cuda_comm_init_rank": (C.c_int, [C.c_int, C.c_int, C.c_void_p]),
+    "stan_cuda_comm_world_size": (C.c_int, []),
+    "stan_cuda_comm_destroy": (None, []),
+    "stan_cuda_data_create": (C.c_int, [C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64,
+                                        C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "stan_cuda_data_destroy": (None, [C.c_void_p]),
+    "stan_cuda_data_params_len": (C.c_int64, [C.c_void_p]),
+    "stan_cuda_data_result_len": (C.c_int64, [C.c_void_p]),
+    "stan_cuda_data_kpad": (C.c_int64, [C.c_void_p]),
+    "stan_cuda_data_algorithmic_bytes": (C.c_int64, [C.c_void_p]),
+    "stan_cuda_glm_launch": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "stan_cuda_allreduce": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p]),
+    "stan_cuda_data_launches_per_eval": (C.c_int, [C.c_void_p]),
+}
+
+
+def bind(lib):
+    """Attach restype/argtypes for every exported entry point; raises if one is missing."""
+    for name, (restype, argtypes) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = restype
+        fn.argtypes = argtypes
+    return lib

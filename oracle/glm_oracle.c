@@ -1,0 +1,196 @@
+/* oracle/glm_oracle.c -- TEST INFRASTRUCTURE, not product code.
+ *
+ * Plain-C CPU restatement of the reference's algorithm for the hot path, one function per
+ * reference function.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg
+ * may load it (as the checker); the product path (math_b200/, stan/math/cuda/) never does.
+ *
+ * Parity status: PINNED.  tests/test_oracle.py checks this file against
+ *   (a) the reference's own known-answer vectors for normal_lpdf
+ *       (test/prob/normal/normal_test.hpp:11-40),
+ *   (b) the fixed fixtures of the reference's GLM unit tests
+ *       (test/unit/math/rev/mat/prob/{bernoulli_logit,poisson_log,normal_id}_glm_*_test.cpp),
+ *       whose expected values are stored in tests/golden/ as produced by the reference itself
+ *       (oracle/_ref/libstanref.so, generator tests/golden/make_golden.py),
+ *   (c) the compiled reference on random inputs whenever oracle/_ref/libstanref.so is present.
+ *
+ * It takes the same argument structs as the product's C ABI (include/stan_cuda.h) so a test can
+ * hand identical arguments to both.  Sums run sequentially in double, in row order; the
+ * reference sums in Eigen's packet order -- both are within a few ulp * sqrt(N) of the exact
+ * sum, far inside the 1e-10 parity bar.
+ */
+#include <math.h>
+#include <stddef.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#include "../include/stan_cuda.h"
+
+/* stan/math/prim/scal/fun/constants.hpp: NEG_LOG_SQRT_TWO_PI = -log(sqrt(2*pi)) */
+static const double ORACLE_NEG_LOG_SQRT_TWO_PI = -0.91893853320467274178032973640561763986;
+
+static double x_at(const stan_cuda_glm_args* a, int64_t i, int64_t j) {
+  return a->x_row_major ? a->x[i * a->ldx + j] : a->x[j * a->ldx + i];
+}
+
+static double y_at(const stan_cuda_glm_args* a, int64_t i) {
+  return a->y_is_double ? ((const double*)a->y)[i] : (double)((const int32_t*)a->y)[i];
+}
+
+/* eta_i = sum_j x_ij beta_j, accumulated column by column exactly like Eigen's col-major GEMV
+ * (bernoulli_logit_glm_lpmf.hpp:92, poisson_log_glm_lpmf.hpp:91, normal_id_glm_lpdf.hpp:108) */
+static double* linear_predictor(const stan_cuda_glm_args* a) {
+  double* eta = (double*)calloc((size_t)(a->n > 0 ? a->n : 1), sizeof(double));
+  if (!eta) return NULL;
+  for (int64_t j = 0; j < a->k; ++j) {
+    const double b = a->beta[j];
+    for (int64_t i = 0; i < a->n; ++i) eta[i] += x_at(a, i, j) * b;
+  }
+  return eta;
+}
+
+/* dbeta = X^T d  (bernoulli :123, poisson :117, normal_id :125-127) */
+static void xt_times(const stan_cuda_glm_args* a, const double* d, double* out) {
+  for (int64_t j = 0; j < a->k; ++j) {
+    double s = 0.0;
+    for (int64_t i = 0; i < a->n; ++i) s += x_at(a, i, j) * d[i];
+    out[j] = s;
+  }
+}
+
+static void write_dalpha(const stan_cuda_glm_args* a, const double* d, double sum_d) {
+  if (!(a->flags & STAN_CUDA_NEED_DALPHA) || !a->dalpha) return;
+  if (a->alpha_len == 1) {
+    a->dalpha[0] = sum_d;
+  } else {
+    for (int64_t i = 0; i < a->n; ++i) a->dalpha[i] = d[i];
+  }
+}
+
+/* stan/math/prim/mat/prob/bernoulli_logit_glm_lpmf.hpp:80-135 */
+static int bernoulli_logit_glm(const stan_cuda_glm_args* a, double* d) {
+  static const double cutoff = 20.0; /* :98 */
+  double logp = 0.0, sum_d = 0.0;
+  double* eta = linear_predictor(a);
+  if (!eta) return STAN_CUDA_ERR_ARG;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const double sign = 2.0 * y_at(a, i) - 1.0;                              /* :90 */
+    const double al = a->alpha_len == 1 ? a->alpha[0] : a->alpha[i];
+    const double ytheta = sign * (eta[i] + al);                              /* :93-94 */
+    const double e = exp(-ytheta);                                           /* :100 */
+    logp += ytheta > cutoff ? -e : (ytheta < -cutoff ? ytheta : -log1p(e)); /* :101-104 */
+    d[i] = ytheta > cutoff ? -e : (ytheta < -cutoff ? sign : sign * e / (e + 1.0)); /* :115-121 */
+    sum_d += d[i];
+  }
+  free(eta);
+  if (a->lp) *a->lp = (a->flags & STAN_CUDA_LP_MAIN) ? logp : 0.0;
+  if (a->aux) { a->aux[0] = sum_d; a->aux[1] = 0; a->aux[2] = 0; a->aux[3] = 0; }
+  write_dalpha(a, d, sum_d);
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;               /* :106 */
+}
+
+/* stan/math/prim/mat/prob/poisson_log_glm_lpmf.hpp:82-129 */
+static int poisson_log_glm(const stan_cuda_glm_args* a, double* d) {
+  double sum_d = 0.0, lg = 0.0, main_term = 0.0;
+  double* theta = linear_predictor(a);
+  if (!theta) return STAN_CUDA_ERR_ARG;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const double y = y_at(a, i);
+    const double th = theta[i] + (a->alpha_len == 1 ? a->alpha[0] : a->alpha[i]); /* :92 */
+    const double e = exp(th);
+    d[i] = y - e;                                                            /* :94-95 */
+    sum_d += d[i];                                                           /* :96 */
+    lg += lgamma(y + 1.0);                                                   /* :104 */
+    main_term += y * th - e;                                                 /* :110-111 */
+  }
+  free(theta);
+  double logp = 0.0;
+  if (a->flags & STAN_CUDA_LP_CONST) logp -= lg;                             /* :102-108 */
+  if (a->flags & STAN_CUDA_LP_MAIN) logp += main_term;                       /* :109-112 */
+  if (a->lp) *a->lp = logp;
+  if (a->aux) { a->aux[0] = sum_d; a->aux[1] = 0; a->aux[2] = 0; a->aux[3] = lg; }
+  write_dalpha(a, d, sum_d);
+  return isfinite(sum_d) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;               /* :97 */
+}
+
+/* stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:89-172 */
+static int normal_id_glm(const stan_cuda_glm_args* a, double* m) {
+  double sum_m = 0.0, sum_s2 = 0.0, sum_log_sigma = 0.0;
+  double* mu = linear_predictor(a);
+  if (!mu) return STAN_CUDA_ERR_ARG;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const double sg = a->sigma_len == 1 ? a->sigma[0] : a->sigma[i];
+    const double inv_sigma = 1.0 / sg;                                       /* :100 */
+    const double al = a->alpha_len == 1 ? a->alpha[0] : a->alpha[i];
+    const double s = (y_at(a, i) - mu[i] - al) * inv_sigma;                  /* :108-111 */
+    m[i] = inv_sigma * s;                                                    /* :117 */
+    sum_m += m[i];
+    sum_s2 += s * s;                                                         /* :138,:141 */
+    if (a->sigma_len != 1) sum_log_sigma += log(sg);                         /* :164 */
+    if ((a->flags & STAN_CUDA_NEED_DY) && a->dy) a->dy[i] = -m[i];            /* :118-120 */
+    if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma && a->sigma_len != 1)
+      a->dsigma[i] = (s * s - 1.0) * inv_sigma;                              /* :139 */
+  }
+  free(mu);
+  if (a->sigma_len == 1) {
+    sum_log_sigma = (double)a->n * log(a->sigma[0]);                         /* :166 */
+    if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma)
+      a->dsigma[0] = (sum_s2 - (double)a->n) * (1.0 / a->sigma[0]);          /* :142-143 */
+  }
+  double logp = 0.0;
+  if (a->flags & STAN_CUDA_LP_CONST) logp += ORACLE_NEG_LOG_SQRT_TWO_PI * (double)a->n; /* :161 */
+  if (a->flags & STAN_CUDA_LP_SCALE) logp -= sum_log_sigma;                  /* :163-168 */
+  if (a->flags & STAN_CUDA_LP_MAIN) logp -= 0.5 * sum_s2;                    /* :170 */
+  if (a->lp) *a->lp = logp;
+  if (a->aux) { a->aux[0] = sum_m; a->aux[1] = sum_s2; a->aux[2] = sum_log_sigma; a->aux[3] = 0; }
+  write_dalpha(a, m, sum_m);
+  return isfinite(sum_s2) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;              /* :150 */
+}
+
+int oracle_glm_eval(const stan_cuda_glm_args* a) {
+  if (!a || a->n < 0 || a->k < 0) return STAN_CUDA_ERR_ARG;
+  if (a->alpha_len != 1 && a->alpha_len != a->n) return STAN_CUDA_ERR_ARG;
+  double* d = (double*)calloc((size_t)(a->n > 0 ? a->n : 1), sizeof(double));
+  if (!d) return STAN_CUDA_ERR_ARG;
+  int rc;
+  switch (a->family) {
+    case STAN_CUDA_BERNOULLI_LOGIT: rc = bernoulli_logit_glm(a, d); break;
+    case STAN_CUDA_POISSON_LOG: rc = poisson_log_glm(a, d); break;
+    case STAN_CUDA_NORMAL_ID:
+      if (a->sigma_len != 1 && a->sigma_len != a->n) { free(d); return STAN_CUDA_ERR_ARG; }
+      rc = normal_id_glm(a, d);
+      break;
+    default: free(d); return STAN_CUDA_ERR_ARG;
+  }
+  if (rc >= 0 && (a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) xt_times(a, d, a->dbeta);
+  free(d);
+  return rc;
+}
+
+/* stan/math/prim/scal/prob/normal_lpdf.hpp:67-110.  Scalar operands accumulate their partial
+ * over n through broadcast_array (prim/scal/meta/broadcast_array.hpp:9-33). */
+int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a) {
+  if (!a || a->n < 0) return STAN_CUDA_ERR_ARG;
+  double logp = 0.0;
+  const int ym = a->y_len != 1, mm = a->mu_len != 1, sm = a->sigma_len != 1;
+  const int need_mu = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dmu;
+  const int need_sigma = (a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma;
+  const int need_y = (a->flags & STAN_CUDA_NEED_DY) && a->dy;
+  if (need_mu) for (int64_t i = 0; i < a->mu_len; ++i) a->dmu[i] = 0.0;
+  if (need_sigma) for (int64_t i = 0; i < a->sigma_len; ++i) a->dsigma[i] = 0.0;
+  if (need_y) for (int64_t i = 0; i < a->y_len; ++i) a->dy[i] = 0.0;
+  for (int64_t n = 0; n < a->n; ++n) {
+    const double sg = a->sigma[sm ? n : 0];
+    const double inv_sigma = 1.0 / sg;                                         /* :72 */
+    const double z = (a->y[ym ? n : 0] - a->mu[mm ? n : 0]) * inv_sigma;        /* :82-83 */
+    const double z2 = z * z;
+    if (a->flags & STAN_CUDA_LP_CONST) logp += ORACLE_NEG_LOG_SQRT_TWO_PI;     /* :89-91 */
+    if (a->flags & STAN_CUDA_LP_SCALE) logp -= log(sg);                        /* :92-94 */
+    if (a->flags & STAN_CUDA_LP_MAIN) logp += -0.5 * z2;                       /* :95-97 */
+    const double scaled_diff = inv_sigma * z;                                  /* :99 */
+    if (need_y) a->dy[ym ? n : 0] -= scaled_diff;                              /* :100-102 */
+    if (need_mu) a->dmu[mm ? n : 0] += scaled_diff;                            /* :103-105 */
+    if (need_sigma) a->dsigma[sm ? n : 0] += -inv_sigma + inv_sigma * z2;      /* :106-109 */
+  }
+  if (a->lp) *a->lp = logp;
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}

@@ -1,0 +1,312 @@
+"""oracle/loader.py -- TEST INFRASTRUCTURE, not product code.
+
+ctypes front-ends of the two CPU checkers:
+
+* ``oracle_*``  -> oracle/liboracle.so    (plain-C restatement, oracle/glm_oracle.c)
+* ``ref_*``     -> oracle/_ref/libstanref.so (the compiled, unmodified reference behind a C shim,
+                   oracle/ref_shim.cpp; present only if it was built where /root/reference exists)
+
+Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline / --impl reference) import this.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from math_b200 import _abi
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "liboracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libstanref.so")
+
+_oracle = None
+_ref = None
+
+
+def build_oracle():
+    subprocess.run(["make", "-s", "-C", HERE, "oracle"], check=True)
+
+
+def oracle_lib():
+    global _oracle
+    if _oracle is None:
+        if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
+                os.path.join(HERE, "glm_oracle.c")):
+            build_oracle()
+        lib = C.CDLL(ORACLE_SO)
+        lib.oracle_glm_eval.restype = C.c_int
+        lib.oracle_glm_eval.argtypes = [C.POINTER(_abi.GlmArgs)]
+        lib.oracle_normal_lpdf_eval.restype = C.c_int
+        lib.oracle_normal_lpdf_eval.argtypes = [C.POINTER(_abi.NormalArgs)]
+        _oracle = lib
+    return _oracle
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        lib = C.CDLL(REF_SO)
+        dp, vp, i, l = C.c_void_p, C.c_void_p, C.c_int, C.c_long
+        lib.stanref_glm.restype = i
+        lib.stanref_glm.argtypes = [i, i, l, l, dp, vp, dp, l, dp, dp, l, i, dp, dp, dp, dp, dp, dp,
+                                    C.c_char_p, i]
+        lib.stanref_glm_value.restype = i
+        lib.stanref_glm_value.argtypes = [i, i, l, l, dp, vp, dp, l, dp, dp, l, dp, C.c_char_p, i]
+        lib.stanref_normal_lpdf.restype = i
+        lib.stanref_normal_lpdf.argtypes = [i, l, dp, dp, l, dp, l, i, dp, dp, dp, dp, dp,
+                                            C.c_char_p, i]
+        lib.stanref_normal_lpdf_value.restype = i
+        lib.stanref_normal_lpdf_value.argtypes = [i, l, dp, dp, l, dp, l, dp, C.c_char_p, i]
+        lib.stanref_init_threads.restype = i
+        lib.stanref_init_threads.argtypes = [i]
+        lib.stanref_shards_create.restype = C.c_void_p
+        lib.stanref_shards_create.argtypes = [i, l, l, dp, vp, i]
+        lib.stanref_shards_free.restype = None
+        lib.stanref_shards_free.argtypes = [C.c_void_p]
+        lib.stanref_shards_eval.restype = i
+        lib.stanref_shards_eval.argtypes = [C.c_void_p, dp, dp, dp, dp, dp, dp, dp, dp, dp,
+                                            C.c_char_p, i]
+        lib.stanref_version.restype = C.c_char_p
+        _ref = lib
+    return _ref
+
+
+# ------------------------------------------------------------------------------------------
+def _f64(a):
+    return np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)))
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+def prep_glm(family, x, y, alpha, beta, sigma=None):
+    """Normalise GLM inputs: x -> column-major f64 (n,k); y -> int32 or f64; vectors -> f64."""
+    fam = _abi.FAMILIES[family] if isinstance(family, str) else family
+    x = np.asfortranarray(np.asarray(x, dtype=np.float64))
+    if x.ndim != 2:
+        raise ValueError("x must be 2-D")
+    if fam == _abi.NORMAL_ID:
+        y = _f64(y)
+    else:
+        y = np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+    alpha, beta = _f64(alpha), _f64(beta)
+    sigma = _f64(sigma) if sigma is not None else None
+    return fam, x, y, alpha, beta, sigma
+
+
+def glm_args(fam, x, y, alpha, beta, sigma, flags, need_dy=False):
+    """Build a GlmArgs block + its output arrays (kept alive in the returned dict)."""
+    n, k = x.shape
+    out = {
+        "lp": np.zeros(1), "dbeta": np.zeros(max(k, 1)), "dalpha": np.zeros(max(alpha.size, 1)),
+        "dsigma": np.zeros(max(sigma.size if sigma is not None else 1, 1)),
+        "dy": np.zeros(max(n, 1)) if need_dy else None, "aux": np.zeros(4),
+    }
+    a = _abi.GlmArgs()
+    a.family, a.flags, a.n, a.k = fam, flags, n, k
+    a.x, a.ldx, a.x_row_major = x.ctypes.data, max(n, 1), 0
+    a.y, a.y_is_double = y.ctypes.data, int(fam == _abi.NORMAL_ID)
+    a.alpha, a.alpha_len = alpha.ctypes.data, alpha.size
+    a.beta = beta.ctypes.data
+    a.sigma, a.sigma_len = (_ptr(sigma), sigma.size) if sigma is not None else (None, 0)
+    a.lp, a.dbeta, a.dalpha = out["lp"].ctypes.data, out["dbeta"].ctypes.data, out["dalpha"].ctypes.data
+    a.dsigma, a.dy, a.aux = out["dsigma"].ctypes.data, _ptr(out["dy"]), out["aux"].ctypes.data
+    out["_keep"] = (x, y, alpha, beta, sigma)
+    return a, out
+
+
+def _finish_glm(rc, out, fam, n, k, alpha, sigma):
+    res = {"rc": rc, "lp": float(out["lp"][0]), "dbeta": out["dbeta"][:k].copy(),
+           "dalpha": out["dalpha"][:alpha.size].copy(), "aux": out["aux"].copy()}
+    if fam == _abi.NORMAL_ID and sigma is not None:
+        res["dsigma"] = out["dsigma"][:sigma.size].copy()
+    if out["dy"] is not None:
+        res["dy"] = out["dy"][:n].copy()
+    return res
+
+
+def flags_for(fam, propto=False, need_dy=False):
+    """lp summands the reference keeps when every parameter is a var (see ref_shim.cpp):
+    bernoulli: everything is parameter-dependent; poisson<propto=true> drops BOTH the lgamma term
+    and (include_summand<propto, double>) the main term, poisson_log_glm_lpmf.hpp:102-112;
+    normal_id<propto=true> drops N*NEG_LOG_SQRT_TWO_PI, normal_id_glm_lpdf.hpp:160-172."""
+    f = _abi.NEED_DBETA | _abi.NEED_DALPHA | _abi.NEED_DSIGMA | (_abi.NEED_DY if need_dy else 0)
+    if not propto:
+        return f | _abi.LP_ALL
+    if fam == _abi.BERNOULLI_LOGIT:
+        return f | _abi.LP_MAIN
+    if fam == _abi.POISSON_LOG:
+        return f
+    return f | _abi.LP_SCALE | _abi.LP_MAIN
+
+
+def oracle_glm(family, x, y, alpha, beta, sigma=None, propto=False, need_dy=False, flags=None):
+    fam, x, y, alpha, beta, sigma = prep_glm(family, x, y, alpha, beta, sigma)
+    if flags is None:
+        flags = flags_for(fam, propto, need_dy)
+    a, out = glm_args(fam, x, y, alpha, beta, sigma, flags, need_dy)
+    rc = oracle_lib().oracle_glm_eval(C.byref(a))
+    return _finish_glm(rc, out, fam, x.shape[0], x.shape[1], alpha, sigma)
+
+
+class RefError(Exception):
+    def __init__(self, rc, msg):
+        super().__init__(msg)
+        self.rc = rc  # 1 std::domain_error, 2 std::invalid_argument, 3 other
+
+
+def ref_glm(family, x, y, alpha, beta, sigma=None, propto=False, need_dy=False):
+    """Value + reverse-mode gradient through the compiled reference (all parameters var)."""
+    fam, x, y, alpha, beta, sigma = prep_glm(family, x, y, alpha, beta, sigma)
+    n, k = x.shape
+    lp, dbeta, dalpha = np.zeros(1), np.zeros(max(k, 1)), np.zeros(max(alpha.size, 1))
+    dsigma = np.zeros(max(sigma.size, 1)) if sigma is not None else np.zeros(1)
+    dy = np.zeros(max(n, 1))
+    secs = np.zeros(1)
+    err = C.create_string_buffer(512)
+    sg = sigma if sigma is not None else np.ones(1)
+    rc = ref_lib().stanref_glm(fam, int(propto), n, k, x.ctypes.data, y.ctypes.data,
+                               alpha.ctypes.data, alpha.size, beta.ctypes.data, sg.ctypes.data,
+                               sg.size, int(need_dy), lp.ctypes.data, dbeta.ctypes.data,
+                               dalpha.ctypes.data, dsigma.ctypes.data, dy.ctypes.data,
+                               secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    res = {"rc": 0, "lp": float(lp[0]), "dbeta": dbeta[:k].copy(), "dalpha": dalpha[:alpha.size].copy(),
+           "seconds": float(secs[0])}
+    if fam == _abi.NORMAL_ID:
+        res["dsigma"] = dsigma[:sg.size].copy()
+    if need_dy:
+        res["dy"] = dy[:n].copy()
+    return res
+
+
+def ref_glm_value(family, x, y, alpha, beta, sigma=None, propto=False):
+    fam, x, y, alpha, beta, sigma = prep_glm(family, x, y, alpha, beta, sigma)
+    n, k = x.shape
+    lp = np.zeros(1)
+    err = C.create_string_buffer(512)
+    sg = sigma if sigma is not None else np.ones(1)
+    rc = ref_lib().stanref_glm_value(fam, int(propto), n, k, x.ctypes.data, y.ctypes.data,
+                                     alpha.ctypes.data, alpha.size, beta.ctypes.data,
+                                     sg.ctypes.data, sg.size, lp.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return float(lp[0])
+
+
+# ------------------------------------------------------------------------------------------
+def normal_flags(propto=False, need_dy=False):
+    f = _abi.NEED_DALPHA | _abi.NEED_DSIGMA | (_abi.NEED_DY if need_dy else 0)
+    return f | (_abi.LP_SCALE | _abi.LP_MAIN if propto else _abi.LP_ALL)
+
+
+def normal_args(y, mu, sigma, flags, y_is_data=True):
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    n = max(y.size, mu.size, sigma.size) if min(y.size, mu.size, sigma.size) > 0 else 0
+    out = {"lp": np.zeros(1), "dmu": np.zeros(max(mu.size, 1)), "dsigma": np.zeros(max(sigma.size, 1)),
+           "dy": np.zeros(max(y.size, 1)), "_keep": (y, mu, sigma)}
+    a = _abi.NormalArgs()
+    a.flags, a.y_is_data, a.n = flags, int(y_is_data), n
+    a.y, a.y_len, a.mu, a.mu_len = y.ctypes.data, y.size, mu.ctypes.data, mu.size
+    a.sigma, a.sigma_len = sigma.ctypes.data, sigma.size
+    a.lp, a.dmu, a.dsigma, a.dy = (out["lp"].ctypes.data, out["dmu"].ctypes.data,
+                                   out["dsigma"].ctypes.data, out["dy"].ctypes.data)
+    return a, out, (y, mu, sigma)
+
+
+def _finish_normal(rc, out, y, mu, sigma, need_dy):
+    res = {"rc": rc, "lp": float(out["lp"][0]), "dmu": out["dmu"][:mu.size].copy(),
+           "dsigma": out["dsigma"][:sigma.size].copy()}
+    if need_dy:
+        res["dy"] = out["dy"][:y.size].copy()
+    return res
+
+
+def oracle_normal_lpdf(y, mu, sigma, propto=False, need_dy=False, flags=None):
+    if flags is None:
+        flags = normal_flags(propto, need_dy)
+    a, out, (y, mu, sigma) = normal_args(y, mu, sigma, flags)
+    rc = oracle_lib().oracle_normal_lpdf_eval(C.byref(a))
+    return _finish_normal(rc, out, y, mu, sigma, need_dy)
+
+
+def ref_normal_lpdf(y, mu, sigma, propto=False, need_dy=False):
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    n = max(y.size, mu.size, sigma.size)
+    if y.size == 1 and n > 1:
+        y = np.full(n, y[0])
+    lp, dmu, dsigma, dy, secs = np.zeros(1), np.zeros(mu.size), np.zeros(sigma.size), np.zeros(n), np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_normal_lpdf(int(propto), n, y.ctypes.data, mu.ctypes.data, mu.size,
+                                       sigma.ctypes.data, sigma.size, int(need_dy), lp.ctypes.data,
+                                       dmu.ctypes.data, dsigma.ctypes.data, dy.ctypes.data,
+                                       secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    res = {"rc": 0, "lp": float(lp[0]), "dmu": dmu, "dsigma": dsigma, "seconds": float(secs[0])}
+    if need_dy:
+        res["dy"] = dy
+    return res
+
+
+def ref_normal_lpdf_value(y, mu, sigma, propto=False):
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    lp = np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_normal_lpdf_value(int(propto), y.size, y.ctypes.data, mu.ctypes.data,
+                                             mu.size, sigma.ctypes.data, sigma.size,
+                                             lp.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return float(lp[0])
+
+
+# ------------------------------------------------------------------------------------------
+class RefShards:
+    """Row-sharded GLM (or J-shard hierarchical GLM) evaluated through the reference's map_rect
+    with TBB threads: the north star's CPU baseline (Eigen + TBB map_rect_concurrent)."""
+
+    def __init__(self, family, x, y, n_shards, n_threads=-1):
+        fam, x, y, _, _, _ = prep_glm(family, x, y, [0.0], np.zeros(np.asarray(x).shape[1]))
+        n, k = x.shape
+        if n % n_shards:
+            raise ValueError("map_rect needs equal-sized jobs: n %% n_shards != 0")
+        self.fam, self.n, self.k, self.n_shards = fam, n, k, n_shards
+        self.threads = ref_lib().stanref_init_threads(n_threads)
+        self.h = ref_lib().stanref_shards_create(fam, n, k, x.ctypes.data, y.ctypes.data, n_shards)
+
+    def eval(self, beta, alpha=None, job_alpha=None, sigma=None):
+        beta = _f64(beta)
+        alpha = _f64(alpha) if alpha is not None else None
+        job_alpha = _f64(job_alpha) if job_alpha is not None else None
+        sigma = _f64(sigma) if sigma is not None else np.ones(1)
+        lp, dbeta = np.zeros(1), np.zeros(self.k)
+        dalpha = np.zeros(self.n_shards if job_alpha is not None else 1)
+        dsigma, secs = np.zeros(1), np.zeros(1)
+        err = C.create_string_buffer(512)
+        rc = ref_lib().stanref_shards_eval(self.h, beta.ctypes.data, _ptr(alpha), _ptr(job_alpha),
+                                           sigma.ctypes.data, lp.ctypes.data, dbeta.ctypes.data,
+                                           dalpha.ctypes.data, dsigma.ctypes.data, secs.ctypes.data,
+                                           err, 512)
+        if rc != 0:
+            raise RefError(rc, err.value.decode())
+        return {"lp": float(lp[0]), "dbeta": dbeta, "dalpha": dalpha, "dsigma": dsigma,
+                "seconds": float(secs[0])}
+
+    def close(self):
+        if self.h:
+            ref_lib().stanref_shards_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
