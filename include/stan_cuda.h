@@ -42,6 +42,12 @@
 
 #include <stdint.h>
 
+#if defined(__GNUC__)
+#define STAN_CUDA_API __attribute__((visibility("default")))
+#else
+#define STAN_CUDA_API
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -124,67 +130,67 @@ typedef struct stan_cuda_stats_t {
 /* ---- context -------------------------------------------------------------------------- */
 /* Use the first n_devices visible devices (0 = all; env STAN_CUDA_DEVICES overrides 0).
  * Idempotent; implied by the first evaluation. */
-int stan_cuda_init(int n_devices);
+STAN_CUDA_API int stan_cuda_init(int n_devices);
 /* Bind this PROCESS to one device (one process per GPU: torchrun LOCAL_RANK). */
-int stan_cuda_init_device(int device_ordinal);
-int stan_cuda_device_count(void);
+STAN_CUDA_API int stan_cuda_init_device(int device_ordinal);
+STAN_CUDA_API int stan_cuda_device_count(void);
 /* Human-readable description of the devices in use (cf. opencl_context.description()). */
-const char* stan_cuda_describe(void);
-const char* stan_cuda_last_error(void); /* thread-local */
-int stan_cuda_stats(stan_cuda_stats_t* out);
-void stan_cuda_stats_reset(void);
+STAN_CUDA_API const char* stan_cuda_describe(void);
+STAN_CUDA_API const char* stan_cuda_last_error(void); /* thread-local */
+STAN_CUDA_API int stan_cuda_stats(stan_cuda_stats_t* out);
+STAN_CUDA_API void stan_cuda_stats_reset(void);
 /* Rows are sharded over all devices of the process only when n*k reaches this many elements
  * (default 1<<24); smaller problems stay on one device. */
-void stan_cuda_set_shard_min_elems(int64_t elems);
+STAN_CUDA_API void stan_cuda_set_shard_min_elems(int64_t elems);
 
 /* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */
-int stan_cuda_glm_eval(const stan_cuda_glm_args* a);
-int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
+STAN_CUDA_API int stan_cuda_glm_eval(const stan_cuda_glm_args* a);
+STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
 
 /* ---- data cache --------------------------------------------------------------------------- */
-int stan_cuda_cache_invalidate(const void* host_ptr); /* drop entries keyed on this x (or y) pointer */
-void stan_cuda_cache_clear(void);
-int64_t stan_cuda_cache_bytes(void);                  /* device bytes held by the cache */
+STAN_CUDA_API int stan_cuda_cache_invalidate(const void* host_ptr); /* drop entries keyed on this x (or y) pointer */
+STAN_CUDA_API void stan_cuda_cache_clear(void);
+STAN_CUDA_API int64_t stan_cuda_cache_bytes(void);                  /* device bytes held by the cache */
 
 /* ---- map_rect shard scope (thread-local) ---------------------------------------------------- */
 /* Inside a scope, evaluations of the calling thread run on `device` and their data is keyed by
  * (call_id, job) instead of by host pointer: the functor rebuilds X from x_r on every call, so
  * its address is not an identity; the immutability contract is map_rect's own
  * (stan/math/prim/mat/functor/map_rect.hpp:97-100). */
-void stan_cuda_shard_scope_enter(int call_id, int job, int device);
-void stan_cuda_shard_scope_exit(void);
+STAN_CUDA_API void stan_cuda_shard_scope_enter(int call_id, int job, int device);
+STAN_CUDA_API void stan_cuda_shard_scope_exit(void);
 
 /* ---- multi-process communicator (one process per GPU) --------------------------------------- */
 /* Rank 0 creates the id; the host plumbing (torch.distributed, MPI, a file) carries the 128 bytes
  * to every rank; every rank then calls comm_init_rank.  After that, sharded evaluations
  * all-reduce [lp-parts, dbeta] across ranks with ncclAllReduce on the evaluation stream. */
-int stan_cuda_comm_unique_id(void* id128);
-int stan_cuda_comm_init_rank(int world_size, int rank, const void* id128);
-int stan_cuda_comm_world_size(void);
-void stan_cuda_comm_destroy(void);
+STAN_CUDA_API int stan_cuda_comm_unique_id(void* id128);
+STAN_CUDA_API int stan_cuda_comm_init_rank(int world_size, int rank, const void* id128);
+STAN_CUDA_API int stan_cuda_comm_world_size(void);
+STAN_CUDA_API void stan_cuda_comm_destroy(void);
 
 /* ---- device-level API (streams and buffers owned by the caller, e.g. torch) ---------------- */
 typedef struct stan_cuda_data* stan_cuda_data_t;
 
 /* Upload + re-layout of (x, y) of one GLM onto the current device: explicit cache fill. */
-int stan_cuda_data_create(int family, int64_t n, int64_t k, const double* x, int64_t ldx,
+STAN_CUDA_API int stan_cuda_data_create(int family, int64_t n, int64_t k, const double* x, int64_t ldx,
                           int x_row_major, const void* y, int y_is_double, stan_cuda_data_t* out);
-void stan_cuda_data_destroy(stan_cuda_data_t d);
+STAN_CUDA_API void stan_cuda_data_destroy(stan_cuda_data_t d);
 /* Number of doubles of the parameter block / result block of a launch. */
-int64_t stan_cuda_data_params_len(stan_cuda_data_t d); /* = k_pad + 2: [beta(k_pad), alpha, sigma] */
-int64_t stan_cuda_data_result_len(stan_cuda_data_t d); /* = k_pad + 4: [lp, sum_d, sum_s2, status, dbeta(k_pad)] */
-int64_t stan_cuda_data_kpad(stan_cuda_data_t d);
-int64_t stan_cuda_data_algorithmic_bytes(stan_cuda_data_t d); /* n*k*8 + n*sizeof(y) */
+STAN_CUDA_API int64_t stan_cuda_data_params_len(stan_cuda_data_t d); /* = k_pad + 2: [beta(k_pad), alpha, sigma] */
+STAN_CUDA_API int64_t stan_cuda_data_result_len(stan_cuda_data_t d); /* = k_pad + 4: [lp, sum_d, sum_s2, status, dbeta(k_pad)] */
+STAN_CUDA_API int64_t stan_cuda_data_kpad(stan_cuda_data_t d);
+STAN_CUDA_API int64_t stan_cuda_data_algorithmic_bytes(stan_cuda_data_t d); /* n*k*8 + n*sizeof(y) */
 /* Enqueue one fused evaluation on `stream` (a cudaStream_t).  d_params / d_result are device
  * pointers (layouts above); d_alpha_vec, d_sigma_vec, d_row_out may be NULL (scalar alpha/sigma,
  * no per-row outputs).  No host synchronisation, no copies. */
-int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params,
+STAN_CUDA_API int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params,
                          const double* d_alpha_vec, const double* d_sigma_vec, double* d_result,
                          double* d_row_dalpha, double* d_row_dsigma, void* stream);
 /* All-reduce (sum) `count` doubles in place across the ranks of the communicator, on `stream`. */
-int stan_cuda_allreduce(double* d_buf, int64_t count, void* stream);
+STAN_CUDA_API int stan_cuda_allreduce(double* d_buf, int64_t count, void* stream);
 /* Number of this library's kernels launched per stan_cuda_glm_launch call for this data. */
-int stan_cuda_data_launches_per_eval(stan_cuda_data_t d);
+STAN_CUDA_API int stan_cuda_data_launches_per_eval(stan_cuda_data_t d);
 
 #ifdef __cplusplus
 }

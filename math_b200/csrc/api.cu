@@ -1,0 +1,449 @@
+// api.cu -- host-level entry points: transparent device cache + evaluation.
+//
+// stan_cuda_glm_eval is what the STAN_CUDA branch of bernoulli_logit_glm_lpmf /
+// poisson_log_glm_lpmf / normal_id_glm_lpdf calls between value_of_rec and ops_partials.build
+// (SURVEY 3.1).  Per evaluation it moves K+2 doubles to the device and K+4 back; X and y are
+// resident from the first call on ("caches the data matrix X and outcome vector y on the device
+// the first time it sees them").  The cache is keyed by host identity plus a content
+// fingerprint, or -- inside a map_rect shard scope -- by (call_id, job), which is the identity
+// the reference's MPI backend already uses for immutable job data
+// (stan/math/prim/mat/functor/mpi_parallel_call.hpp:40-89).
+#include <math.h>
+
+#include <chrono>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <tuple>
+
+#include "context.cuh"
+
+namespace stancuda {
+
+struct Shard {
+  stan_cuda_data* d = nullptr;
+  int64_t row0 = 0;
+};
+
+struct Entry {
+  std::vector<Shard> shards;   // GLM data, one block per device
+  double* vec = nullptr;       // normal_lpdf: cached y
+  int vec_device = -1;
+  uint64_t fingerprint = 0;
+  size_t bytes = 0;
+  ~Entry() {
+    for (Shard& s : shards) free_data_block(s.d);
+    if (vec) {
+      cudaSetDevice(vec_device);
+      cudaFree(vec);
+    }
+  }
+};
+
+// key: (kind, a, b, n, k, ldx, misc)   kind 0 = host pointers, 1 = shard scope, 2 = normal_lpdf y
+typedef std::tuple<int, uintptr_t, uintptr_t, int64_t, int64_t, int64_t, int64_t> Key;
+
+static std::mutex g_cache_mu;
+static std::map<Key, std::shared_ptr<Entry>> g_cache;
+
+struct Scope {
+  bool active = false;
+  int call_id = 0, job = 0, device = 0;
+};
+static thread_local Scope tl_scope;
+
+static uint64_t fnv(uint64_t h, uint64_t v) {
+  for (int i = 0; i < 8; ++i) {
+    h ^= (v >> (8 * i)) & 0xff;
+    h *= 1099511628211ull;
+  }
+  return h;
+}
+
+// Content fingerprint from <= 64 sampled elements of each array: catches an address that is
+// reused for different data (the reference once reverted a transparent GPU cache for
+// exactly this reason, RELEASE-NOTES.txt:36).
+static uint64_t fingerprint_glm(const stan_cuda_glm_args* a) {
+  uint64_t h = 1469598103934665603ull;
+  const int64_t cnt = a->n * a->k;
+  const int64_t step = cnt > 64 ? cnt / 64 : 1;
+  for (int64_t q = 0; q < cnt; q += step) {
+    int64_t i, j;
+    if (a->x_row_major) { i = q / a->k; j = q % a->k; } else { j = q / a->n; i = q % a->n; }
+    const double v = a->x_row_major ? a->x[i * a->ldx + j] : a->x[j * a->ldx + i];
+    uint64_t bits;
+    memcpy(&bits, &v, 8);
+    h = fnv(h, bits);
+  }
+  const int64_t ystep = a->n > 64 ? a->n / 64 : 1;
+  for (int64_t i = 0; i < a->n; i += ystep) {
+    uint64_t bits = 0;
+    if (a->y_is_double) memcpy(&bits, static_cast<const double*>(a->y) + i, 8);
+    else bits = uint64_t(uint32_t(static_cast<const int32_t*>(a->y)[i]));
+    h = fnv(h, bits);
+  }
+  return h;
+}
+
+static uint64_t fingerprint_vec(const double* v, int64_t n) {
+  uint64_t h = 1469598103934665603ull;
+  const int64_t step = n > 128 ? n / 128 : 1;
+  for (int64_t i = 0; i < n; i += step) {
+    uint64_t bits;
+    memcpy(&bits, v + i, 8);
+    h = fnv(h, bits);
+  }
+  return h;
+}
+
+// Which devices serve this call: the scope's device, all devices (row-sharded) or the first.
+static std::vector<int> pick_devices(int64_t n, int64_t k) {
+  Context& c = context();
+  std::vector<int> out;
+  if (tl_scope.active) {
+    out.push_back(c.devices[size_t(tl_scope.device) % c.devices.size()]);
+  } else if (c.devices.size() > 1 && n * (k > 0 ? k : 1) >= c.shard_min_elems && n >= int64_t(c.devices.size()) * 1024) {
+    out = c.devices;
+  } else {
+    out.push_back(c.devices[0]);
+  }
+  return out;
+}
+
+static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* out) {
+  Key key;
+  if (tl_scope.active) {
+    key = Key(1, uintptr_t(tl_scope.call_id), uintptr_t(tl_scope.job), a->n, a->k, a->family, tl_scope.device);
+  } else {
+    key = Key(0, uintptr_t(a->x), uintptr_t(a->y), a->n, a->k, a->ldx,
+              int64_t(a->family) * 4 + a->x_row_major * 2 + a->y_is_double);
+  }
+  const uint64_t fp = fingerprint_glm(a);
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  auto it = g_cache.find(key);
+  if (it != g_cache.end() && it->second->fingerprint == fp) {
+    counters().cache_hits.fetch_add(1, std::memory_order_relaxed);
+    *out = it->second;
+    return STAN_CUDA_OK;
+  }
+  counters().cache_misses.fetch_add(1, std::memory_order_relaxed);
+  if (it != g_cache.end()) g_cache.erase(it);  // stale: same identity, different content
+  auto t0 = std::chrono::steady_clock::now();
+  std::shared_ptr<Entry> e = std::make_shared<Entry>();
+  e->fingerprint = fp;
+  const std::vector<int> devs = pick_devices(a->n, a->k);
+  const int64_t G = int64_t(devs.size());
+  const int64_t per = (a->n + G - 1) / G;
+  for (int64_t g = 0; g < G; ++g) {
+    const int64_t r0 = g * per;
+    const int64_t rows = (a->n - r0 < per) ? (a->n - r0) : per;
+    if (rows <= 0) break;
+    ThreadDev* td;
+    SC_TRY(thread_dev(devs[g], &td));
+    Shard s;
+    s.row0 = r0;
+    SC_TRY(make_data_block(devs[g], a->family, rows, a->k, a->x, a->ldx, a->x_row_major, a->y, a->y_is_double,
+                           r0, td->stream, &s.d));
+    e->bytes += s.d->bytes;
+    e->shards.push_back(s);
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  counters().last_fill_ms.store(std::chrono::duration<double, std::milli>(t1 - t0).count());
+  g_cache[key] = e;
+  *out = e;
+  return STAN_CUDA_OK;
+}
+
+static int check_glm_args(const stan_cuda_glm_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null args");
+  if (a->family < 0 || a->family > 2) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: unknown family");
+  if (a->n < 0 || a->k < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: negative size");
+  if (a->n > 0 && (!a->y || (!a->x && a->k > 0))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null x or y");
+  if (a->k > 0 && !a->beta) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null beta");
+  if (!a->alpha || (a->alpha_len != 1 && a->alpha_len != a->n))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: alpha_len must be 1 or n");
+  if (a->family == STAN_CUDA_NORMAL_ID) {
+    if (!a->sigma || (a->sigma_len != 1 && a->sigma_len != a->n))
+      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: sigma_len must be 1 or n");
+    if (!a->y_is_double) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: normal_id needs double y");
+  } else if (a->y_is_double) {
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: bernoulli/poisson need int32 y");
+  }
+  if (a->k > 0 && a->ldx < (a->x_row_major ? a->k : a->n))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: ldx too small");
+  return STAN_CUDA_OK;
+}
+
+struct ShardRun {
+  ThreadDev* td = nullptr;
+  double *d_params = nullptr, *d_result = nullptr, *d_alpha = nullptr, *d_sigma = nullptr, *d_rowa = nullptr,
+         *d_rows = nullptr;
+};
+
+int glm_eval(const stan_cuda_glm_args* a) {
+  SC_TRY(check_glm_args(a));
+  if (a->n == 0) {  // size_zero(y): the reference returns 0 before touching anything (:72-74)
+    if (a->lp) *a->lp = 0.0;
+    if (a->dbeta) for (int64_t j = 0; j < a->k; ++j) a->dbeta[j] = 0.0;
+    return STAN_CUDA_OK;
+  }
+  SC_TRY(ensure_init());
+  std::shared_ptr<Entry> e;
+  SC_TRY(get_glm_entry(a, &e));
+  const size_t S = e->shards.size();
+  const bool alpha_vec = a->alpha_len != 1;
+  const bool sigma_vec = a->family == STAN_CUDA_NORMAL_ID && a->sigma_len != 1;
+  const bool want_rowa = ((a->flags & STAN_CUDA_NEED_DALPHA) && alpha_vec && a->dalpha) ||
+                         ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID);
+  const bool want_rows = (a->flags & STAN_CUDA_NEED_DSIGMA) && sigma_vec && a->dsigma;
+  const int world = comm_world_size();
+  if (world > 1 && S > 1) return fail(STAN_CUDA_ERR_STATE, "multi-process communicator with several devices per process");
+
+  std::vector<ShardRun> runs(S);
+  const int kpad = e->shards[0].d->t.kpad;
+  const size_t np = size_t(kpad) + 2, nr = size_t(kpad) + 4;
+  for (size_t s = 0; s < S; ++s) {
+    stan_cuda_data* d = e->shards[s].d;
+    const int64_t rows = d->n, r0 = e->shards[s].row0;
+    ShardRun& run = runs[s];
+    SC_TRY(thread_dev(d->device, &run.td));
+    ThreadDev* td = run.td;
+    SC_CUDA(cudaSetDevice(d->device));
+    SC_TRY(td->reserve_host(np + nr));
+    size_t need = np + nr + 8;
+    const size_t rows_al = (size_t(rows) + 1) & ~size_t(1);
+    if (alpha_vec) need += rows_al;
+    if (sigma_vec) need += rows_al;
+    if (want_rowa) need += rows_al;
+    if (want_rows) need += rows_al;
+    SC_TRY(td->reserve_dev(need));
+    double* p = td->d_buf;
+    run.d_params = p; p += (np + 1) & ~size_t(1);
+    run.d_result = p; p += (nr + 1) & ~size_t(1);
+    if (alpha_vec) { run.d_alpha = p; p += rows_al; }
+    if (sigma_vec) { run.d_sigma = p; p += rows_al; }
+    if (want_rowa) { run.d_rowa = p; p += rows_al; }
+    if (want_rows) { run.d_rows = p; p += rows_al; }
+    double* hp = td->h_pinned;
+    for (int j = 0; j < kpad; ++j) hp[j] = j < a->k ? a->beta[j] : 0.0;
+    hp[kpad] = alpha_vec ? 0.0 : a->alpha[0];
+    hp[kpad + 1] = (a->family == STAN_CUDA_NORMAL_ID && !sigma_vec) ? a->sigma[0] : 1.0;
+    SC_CUDA(cudaMemcpyAsync(run.d_params, hp, np * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    if (alpha_vec)
+      SC_CUDA(cudaMemcpyAsync(run.d_alpha, a->alpha + r0, size_t(rows) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    if (sigma_vec)
+      SC_CUDA(cudaMemcpyAsync(run.d_sigma, a->sigma + r0, size_t(rows) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    LaunchIO io{a->flags, run.d_params, run.d_alpha, run.d_sigma, run.d_result, run.d_rowa, run.d_rows};
+    SC_TRY(launch_glm(d, io, &td->ws, td->stream));
+  }
+  // combine the additive result blocks of the row shards
+  if (S > 1) {
+    std::vector<int> devs(S);
+    std::vector<double*> bufs(S);
+    std::vector<cudaStream_t> streams(S);
+    for (size_t s = 0; s < S; ++s) {
+      devs[s] = e->shards[s].d->device;
+      bufs[s] = runs[s].d_result;
+      streams[s] = runs[s].td->stream;
+    }
+    SC_TRY(comm_allreduce_local(devs, bufs, int64_t(nr), streams));
+  } else if (world > 1) {
+    SC_CUDA(cudaSetDevice(e->shards[0].d->device));
+    SC_TRY(comm_allreduce_rank(runs[0].d_result, int64_t(nr), runs[0].td->stream));
+  }
+  // results back
+  for (size_t s = 0; s < S; ++s) {
+    stan_cuda_data* d = e->shards[s].d;
+    const int64_t rows = d->n, r0 = e->shards[s].row0;
+    ThreadDev* td = runs[s].td;
+    SC_CUDA(cudaSetDevice(d->device));
+    if (s == 0)
+      SC_CUDA(cudaMemcpyAsync(td->h_pinned + np, runs[s].d_result, nr * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+    if (want_rowa) {
+      double* dst = (alpha_vec && (a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha) ? a->dalpha : a->dy;
+      SC_CUDA(cudaMemcpyAsync(dst + r0, runs[s].d_rowa, size_t(rows) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+    }
+    if (want_rows)
+      SC_CUDA(cudaMemcpyAsync(a->dsigma + r0, runs[s].d_rows, size_t(rows) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  }
+  for (size_t s = 0; s < S; ++s) {
+    SC_CUDA(cudaSetDevice(e->shards[s].d->device));
+    SC_CUDA(cudaStreamSynchronize(runs[s].td->stream));
+  }
+  const double* res = runs[0].td->h_pinned + np;
+  if (a->lp) *a->lp = res[0];
+  if ((a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) memcpy(a->dbeta, res + 4, size_t(a->k) * sizeof(double));
+  if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha && !alpha_vec) a->dalpha[0] = res[1];
+  if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma && a->family == STAN_CUDA_NORMAL_ID && !sigma_vec)
+    a->dsigma[0] = res[2];
+  if ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID) {
+    // dy = -mu_derivative (normal_id_glm_lpdf.hpp:118-120); the kernel wrote mu_derivative
+    const bool via_dalpha = alpha_vec && (a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha;
+    const double* src = via_dalpha ? a->dalpha : a->dy;
+    for (int64_t i = 0; i < a->n; ++i) a->dy[i] = -src[i];
+  }
+  if (a->aux) {
+    a->aux[0] = res[1];
+    a->aux[1] = res[3];
+    a->aux[2] = 0.0;
+    a->aux[3] = e->shards[0].d->lgamma_sum;
+  }
+  counters().evals.fetch_add(1, std::memory_order_relaxed);
+  return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
+}  // namespace stancuda
+
+// =============================================================================================
+// normal_lpdf
+// =============================================================================================
+namespace stancuda {
+
+static int get_vec_entry(const double* v, int64_t n, int device, cudaStream_t stream, std::shared_ptr<Entry>* out) {
+  Key key(2, uintptr_t(v), 0, n, 0, 0, device);
+  const uint64_t fp = fingerprint_vec(v, n);
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  auto it = g_cache.find(key);
+  if (it != g_cache.end() && it->second->fingerprint == fp) {
+    counters().cache_hits.fetch_add(1, std::memory_order_relaxed);
+    *out = it->second;
+    return STAN_CUDA_OK;
+  }
+  counters().cache_misses.fetch_add(1, std::memory_order_relaxed);
+  if (it != g_cache.end()) g_cache.erase(it);
+  std::shared_ptr<Entry> e = std::make_shared<Entry>();
+  e->fingerprint = fp;
+  e->vec_device = device;
+  SC_CUDA(cudaSetDevice(device));
+  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->vec), size_t(n) * sizeof(double)));
+  e->bytes = size_t(n) * sizeof(double);
+  SC_CUDA(cudaMemcpyAsync(e->vec, v, size_t(n) * sizeof(double), cudaMemcpyHostToDevice, stream));
+  SC_CUDA(cudaStreamSynchronize(stream));
+  counters().bytes_uploaded.fetch_add(uint64_t(n) * sizeof(double));
+  g_cache[key] = e;
+  *out = e;
+  return STAN_CUDA_OK;
+}
+
+int normal_lpdf_eval(const stan_cuda_normal_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: null args");
+  if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: negative n");
+  if (a->n == 0) {  // size_zero(y, mu, sigma) -> 0 (normal_lpdf.hpp:45-47)
+    if (a->lp) *a->lp = 0.0;
+    return STAN_CUDA_OK;
+  }
+  if (!a->y || !a->mu || !a->sigma) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: null operand");
+  auto ok_len = [&](int64_t len) { return len == 1 || len == a->n; };
+  if (!ok_len(a->y_len) || !ok_len(a->mu_len) || !ok_len(a->sigma_len))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: operand length must be 1 or n");
+  SC_TRY(ensure_init());
+  Context& c = context();
+  const int dev = tl_scope.active ? c.devices[size_t(tl_scope.device) % c.devices.size()] : c.devices[0];
+  ThreadDev* td;
+  SC_TRY(thread_dev(dev, &td));
+  SC_CUDA(cudaSetDevice(dev));
+  const int64_t n = a->n;
+  const bool yv = a->y_len != 1, mv = a->mu_len != 1, sv = a->sigma_len != 1;
+  const bool need_mu = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dmu;
+  const bool need_sigma = (a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma;
+  const bool need_y = (a->flags & STAN_CUDA_NEED_DY) && a->dy;
+  std::shared_ptr<Entry> ycache;
+  if (yv && a->y_is_data) SC_TRY(get_vec_entry(a->y, n, dev, td->stream, &ycache));
+  const size_t nal = (size_t(n) + 1) & ~size_t(1);
+  size_t need = 8;
+  if (yv && !ycache) need += nal;
+  if (mv) need += nal;
+  if (sv) need += nal;
+  if (need_mu && mv) need += nal;
+  if (need_sigma && sv) need += nal;
+  if (need_y && yv) need += nal;
+  SC_TRY(td->reserve_dev(need));
+  SC_TRY(td->reserve_host(8));
+  double* p = td->d_buf;
+  NormalIO io{};
+  io.flags = a->flags;
+  io.n = n;
+  io.result = p; p += 8;
+  io.y_vec = yv; io.mu_vec = mv; io.sigma_vec = sv;
+  io.y0 = a->y[0]; io.mu0 = a->mu[0]; io.sigma0 = a->sigma[0];
+  if (yv) {
+    if (ycache) {
+      io.y = ycache->vec;
+    } else {
+      SC_CUDA(cudaMemcpyAsync(p, a->y, size_t(n) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+      io.y = p; p += nal;
+    }
+  }
+  if (mv) {
+    SC_CUDA(cudaMemcpyAsync(p, a->mu, size_t(n) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    io.mu = p; p += nal;
+  }
+  if (sv) {
+    SC_CUDA(cudaMemcpyAsync(p, a->sigma, size_t(n) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    io.sigma = p; p += nal;
+  }
+  if (need_mu && mv) { io.dmu_row = p; p += nal; }
+  if (need_sigma && sv) { io.dsigma_row = p; p += nal; }
+  if (need_y && yv) { io.dy_row = p; p += nal; }
+  SC_TRY(launch_normal_lpdf(io, &td->ws, dev, td->stream));
+  SC_CUDA(cudaMemcpyAsync(td->h_pinned, io.result, 4 * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  if (io.dmu_row) SC_CUDA(cudaMemcpyAsync(a->dmu, io.dmu_row, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  if (io.dsigma_row) SC_CUDA(cudaMemcpyAsync(a->dsigma, io.dsigma_row, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  if (io.dy_row) SC_CUDA(cudaMemcpyAsync(a->dy, io.dy_row, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  SC_CUDA(cudaStreamSynchronize(td->stream));
+  const double* res = td->h_pinned;
+  if (a->lp) *a->lp = res[0];
+  if (need_mu && !mv) a->dmu[0] = res[1];
+  if (need_y && !yv) a->dy[0] = -res[1];
+  if (need_sigma && !sv) a->dsigma[0] = res[2];
+  counters().evals.fetch_add(1, std::memory_order_relaxed);
+  return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
+}  // namespace stancuda
+
+using namespace stancuda;
+
+extern "C" {
+
+int stan_cuda_glm_eval(const stan_cuda_glm_args* a) { return glm_eval(a); }
+int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) { return normal_lpdf_eval(a); }
+
+int stan_cuda_cache_invalidate(const void* host_ptr) {
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  int dropped = 0;
+  for (auto it = g_cache.begin(); it != g_cache.end();) {
+    const Key& k = it->first;
+    const bool by_ptr = std::get<0>(k) != 1;
+    if (by_ptr && (std::get<1>(k) == uintptr_t(host_ptr) || std::get<2>(k) == uintptr_t(host_ptr))) {
+      it = g_cache.erase(it);
+      ++dropped;
+    } else {
+      ++it;
+    }
+  }
+  return dropped;
+}
+
+void stan_cuda_cache_clear(void) {
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  g_cache.clear();
+}
+
+int64_t stan_cuda_cache_bytes(void) {
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  int64_t b = 0;
+  for (auto& kv : g_cache) b += int64_t(kv.second->bytes);
+  return b;
+}
+
+void stan_cuda_shard_scope_enter(int call_id, int job, int device) {
+  tl_scope.active = true;
+  tl_scope.call_id = call_id;
+  tl_scope.job = job;
+  tl_scope.device = device < 0 ? 0 : device;
+}
+
+void stan_cuda_shard_scope_exit(void) { tl_scope.active = false; }
+
+}  // extern "C"

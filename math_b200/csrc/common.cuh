@@ -1,0 +1,123 @@
+// common.cuh -- shared declarations of libstanmath_cuda.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdio>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/stan_cuda.h"
+
+namespace stancuda {
+
+// ---- error plumbing: no exception leaves the library, text goes to a thread-local string ----
+void set_last_error(const std::string& s);
+int fail(int code, const std::string& what);
+int fail_cuda(cudaError_t e, const char* expr, const char* file, int line);
+
+#define SC_CUDA(expr)                                                              \
+  do {                                                                             \
+    cudaError_t _e = (expr);                                                       \
+    if (_e != cudaSuccess) return ::stancuda::fail_cuda(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define SC_TRY(expr)            \
+  do {                          \
+    int _rc = (expr);           \
+    if (_rc < 0) return _rc;    \
+  } while (0)
+
+// ---- tiling of one GLM data block (see DESIGN.md "Data layout in HBM") -----------------------
+// X is stored tile by tile; a tile holds R consecutive rows and all kpad columns, column-major
+// inside the tile:  x_dev[(tile * kpad + col) * R + r].  One tile is one contiguous span, so a
+// single 1-D TMA bulk copy (cp.async.bulk) stages it.  Thread (cg, r) of the fused kernel owns
+// row r and the kc columns [cg*kc, (cg+1)*kc);  C * R == threads,  kpad == C * kc,  kc <= 16.
+constexpr int kMaxKc = 16;
+
+struct Tiling {
+  int threads;  // consumer threads per CTA (128 | 256 | 512)
+  int C;        // column groups (power of two)
+  int kc;       // columns per thread, 1..16
+  int R;        // rows per tile = threads / C (power of two, >= 8)
+  int kpad;     // C * kc >= k
+  int64_t tiles;
+  size_t tile_bytes() const { return size_t(kpad) * R * sizeof(double); }
+};
+
+// Picks C, kc, R for k columns and n rows; returns false if k is outside the fused kernel's range.
+bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t);
+
+struct Workspace {   // per (host thread, device) or per data handle: one launch in flight at a time
+  int device = -1;
+  double* scratch = nullptr;  // [max_grid][kpad_cap + 4] per-CTA partials
+  unsigned int* ticket = nullptr;
+  size_t scratch_doubles = 0;
+};
+int workspace_reserve(Workspace* w, int device, size_t doubles);
+void workspace_free(Workspace* w);
+
+}  // namespace stancuda
+
+// One GLM data block resident on one device.
+struct stan_cuda_data {
+  int device = 0;
+  int family = 0;
+  int64_t n = 0, k = 0;
+  int y_is_double = 0;
+  stancuda::Tiling t{};
+  double* x = nullptr;   // tiled layout, zero padded
+  void* y = nullptr;     // int32 or double, padded to tiles * R
+  double lgamma_sum = 0; // sum lgamma(y+1) (poisson), computed once at fill
+  size_t bytes = 0;
+  stancuda::Workspace ws;  // used by the device-level API (stan_cuda_glm_launch)
+};
+
+namespace stancuda {
+
+struct LaunchIO {
+  uint32_t flags;
+  const double* d_params;     // [kpad] beta, [kpad] alpha, [kpad+1] sigma
+  const double* d_alpha_vec;  // n or null
+  const double* d_sigma_vec;  // n or null
+  double* d_result;           // [kpad + 4]
+  double* d_row_dalpha;       // n or null
+  double* d_row_dsigma;       // n or null
+};
+
+// Enqueue the fused kernel for one data block.  ws must belong to the block's device.
+int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+int sm_count(int device);
+
+// tuning knobs (env STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM; 0 = auto)
+struct Tuning { int threads = 0, stages = 0, ctas_per_sm = 0; };
+const Tuning& tuning();
+
+// relayout kernels (data.cu)
+int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_major, const void* y,
+                    int64_t row0, cudaStream_t stream, uint64_t* bytes_uploaded);
+
+// normal_lpdf kernel (normal_kernel.cu)
+struct NormalIO {
+  uint32_t flags;
+  int64_t n;
+  const double* y; int y_vec;
+  const double* mu; int mu_vec;
+  const double* sigma; int sigma_vec;
+  double y0, mu0, sigma0;     // scalar operands by value
+  double* dmu_row; double* dsigma_row; double* dy_row;  // per-row outputs (vector operands) or null
+  double* result;             // [4]: lp, sum scaled_diff, sum dsigma, witness
+};
+int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream_t stream);
+
+// counters
+struct Counters {
+  std::atomic<uint64_t> cache_hits{0}, cache_misses{0}, bytes_uploaded{0}, evals{0}, launches{0},
+      allreduces{0};
+  std::atomic<double> last_fill_ms{0};
+};
+Counters& counters();
+
+}  // namespace stancuda

@@ -1,0 +1,263 @@
+// data.cu -- cache fill: host (x, y) -> tiled device layout.  Replaces matrix_cl + to_matrix_cl
+// (stan/math/opencl/matrix_cl.hpp:32-454, stan/math/opencl/copy.hpp:37-93) for the GLM data.
+//
+// The device layout is chosen for the fused kernel, not for the host: tile by tile, each tile
+// R rows x kpad columns, column-major inside the tile (see common.cuh / DESIGN.md).  The host
+// matrix (Eigen column-major, or row-major) is streamed through a bounded staging buffer and
+// re-tiled by a kernel, so the fill never needs a second full-size copy of X on the device.
+#include <math.h>
+
+#include <chrono>
+
+#include "context.cuh"
+
+namespace stancuda {
+
+// staging chunk -> tiled X.  Chunk holds rows [0, n) x columns [c0, c0 + nc) of the block:
+//   column-major source: src[jj * src_ld + i]      (src_ld >= n)
+//   row-major source   : src[i * src_ld + c0 + jj] is NOT used; row-major chunks hold rows
+//                        [i0, i0 + ni) x all k columns: src[(i - i0) * src_ld + j]
+__global__ void retile_colmajor_kernel(const double* __restrict__ src, int64_t src_ld, int64_t n, int c0, int nc,
+                                       double* __restrict__ dst, int R, int kpad, int64_t tiles) {
+  const int64_t per_col = tiles * R;
+  const int64_t total = per_col * nc;
+  for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < total;
+       idx += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t jj = idx / per_col;
+    const int64_t i = idx - jj * per_col;  // row index (padded range)
+    const int64_t tile = i / R;
+    const int r = int(i - tile * R);
+    const double v = i < n ? src[jj * src_ld + i] : 0.0;
+    dst[(tile * kpad + c0 + jj) * R + r] = v;
+  }
+}
+
+__global__ void retile_rowmajor_kernel(const double* __restrict__ src, int64_t src_ld, int64_t i0, int64_t ni,
+                                       int k, double* __restrict__ dst, int R, int kpad) {
+  // one thread per destination element of the row range; r fastest so writes coalesce
+  const int64_t total = ni * k;
+  for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < total;
+       idx += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t j = idx / ni;
+    const int64_t ii = idx - j * ni;
+    const int64_t i = i0 + ii;
+    const int64_t tile = i / R;
+    const int r = int(i - tile * R);
+    dst[(tile * kpad + j) * R + r] = src[ii * src_ld + j];
+  }
+}
+
+// sum lgamma(y + 1) over int y: per-block partials in block order, summed on the host in order
+// (poisson_log_glm_lpmf.hpp:102-108 -- depends on data only, so it is computed once per fill).
+__global__ void lgamma_partial_kernel(const int* __restrict__ y, int64_t n, double* __restrict__ partial) {
+  __shared__ double sh[256];
+  double s = 0.0;
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    s += lgamma(double(y[i]) + 1.0);
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int off = 128; off > 0; off >>= 1) {
+    if (int(threadIdx.x) < off) sh[threadIdx.x] += sh[threadIdx.x + off];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+}
+
+static const size_t kStageBytes = size_t(256) << 20;  // staging buffer for the fill
+
+// Upload rows [row0, row0 + d->n) of the host matrix into d (already sized; d->t chosen).
+int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_major, const void* y,
+                    int64_t row0, cudaStream_t stream, uint64_t* bytes_uploaded) {
+  const Tiling& t = d->t;
+  const int64_t n = d->n, k = d->k;
+  SC_CUDA(cudaSetDevice(d->device));
+  const size_t x_bytes = size_t(t.tiles) * t.tile_bytes();
+  const size_t y_elem = d->y_is_double ? sizeof(double) : sizeof(int);
+  const size_t y_bytes = size_t(t.tiles) * t.R * y_elem;
+  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d->x), x_bytes));
+  SC_CUDA(cudaMalloc(&d->y, y_bytes));
+  d->bytes = x_bytes + y_bytes;
+  // zero fill covers the padding columns [k, kpad) (padding rows are written by the retile kernel)
+  if (t.kpad != k || x_row_major) SC_CUDA(cudaMemsetAsync(d->x, 0, x_bytes, stream));
+  SC_CUDA(cudaMemsetAsync(d->y, 0, y_bytes, stream));
+  SC_CUDA(cudaMemcpyAsync(d->y, static_cast<const char*>(y) + size_t(row0) * y_elem, size_t(n) * y_elem,
+                          cudaMemcpyHostToDevice, stream));
+  uint64_t up = uint64_t(n) * y_elem;
+
+  double* stage[2] = {nullptr, nullptr};
+  cudaEvent_t freed[2] = {nullptr, nullptr};
+  int rc = STAN_CUDA_OK;
+  auto cleanup = [&]() {
+    for (int i = 0; i < 2; ++i) {
+      if (stage[i]) cudaFree(stage[i]);
+      if (freed[i]) cudaEventDestroy(freed[i]);
+    }
+  };
+#define SC_CUDA_CLEAN(expr)                                          \
+  do {                                                               \
+    cudaError_t _e = (expr);                                         \
+    if (_e != cudaSuccess) {                                         \
+      rc = fail_cuda(_e, #expr, __FILE__, __LINE__);                 \
+      cleanup();                                                     \
+      return rc;                                                     \
+    }                                                                \
+  } while (0)
+
+  const int blocks = sm_count(d->device) * 8;
+  if (!x_row_major) {
+    // chunk = a range of whole columns (rows row0 .. row0+n of each)
+    int64_t cols_per_chunk = int64_t(kStageBytes / (size_t(n) * sizeof(double)));
+    if (cols_per_chunk < 1) cols_per_chunk = 1;
+    if (cols_per_chunk > k) cols_per_chunk = k;
+    const size_t stage_doubles = size_t(cols_per_chunk) * n;
+    for (int i = 0; i < 2; ++i) {
+      SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&stage[i]), stage_doubles * sizeof(double)));
+      SC_CUDA_CLEAN(cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming));
+    }
+    int which = 0;
+    for (int64_t c0 = 0; c0 < k; c0 += cols_per_chunk, which ^= 1) {
+      const int64_t nc = (k - c0 < cols_per_chunk) ? (k - c0) : cols_per_chunk;
+      SC_CUDA_CLEAN(cudaEventSynchronize(freed[which]));
+      if (ldx == n && row0 == 0) {
+        SC_CUDA_CLEAN(cudaMemcpyAsync(stage[which], x + size_t(c0) * ldx, size_t(nc) * n * sizeof(double),
+                                      cudaMemcpyHostToDevice, stream));
+      } else {
+        SC_CUDA_CLEAN(cudaMemcpy2DAsync(stage[which], size_t(n) * sizeof(double), x + size_t(c0) * ldx + row0,
+                                        size_t(ldx) * sizeof(double), size_t(n) * sizeof(double), size_t(nc),
+                                        cudaMemcpyHostToDevice, stream));
+      }
+      retile_colmajor_kernel<<<blocks, 256, 0, stream>>>(stage[which], n, n, int(c0), int(nc), d->x, t.R, t.kpad,
+                                                        t.tiles);
+      SC_CUDA_CLEAN(cudaGetLastError());
+      SC_CUDA_CLEAN(cudaEventRecord(freed[which], stream));
+      up += uint64_t(nc) * n * sizeof(double);
+    }
+  } else {
+    int64_t rows_per_chunk = int64_t(kStageBytes / (size_t(ldx) * sizeof(double)));
+    if (rows_per_chunk < 1) rows_per_chunk = 1;
+    if (rows_per_chunk > n) rows_per_chunk = n;
+    const size_t stage_doubles = size_t(rows_per_chunk) * ldx;
+    for (int i = 0; i < 2; ++i) {
+      SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&stage[i]), stage_doubles * sizeof(double)));
+      SC_CUDA_CLEAN(cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming));
+    }
+    int which = 0;
+    for (int64_t i0 = 0; i0 < n; i0 += rows_per_chunk, which ^= 1) {
+      const int64_t ni = (n - i0 < rows_per_chunk) ? (n - i0) : rows_per_chunk;
+      SC_CUDA_CLEAN(cudaEventSynchronize(freed[which]));
+      // last row of the chunk may be shorter than ldx in the host allocation: copy (ni-1)*ldx + k
+      const size_t cnt = size_t(ni - 1) * ldx + k;
+      SC_CUDA_CLEAN(cudaMemcpyAsync(stage[which], x + size_t(row0 + i0) * ldx, cnt * sizeof(double),
+                                    cudaMemcpyHostToDevice, stream));
+      retile_rowmajor_kernel<<<blocks, 256, 0, stream>>>(stage[which], ldx, i0, ni, int(k), d->x, t.R, t.kpad);
+      SC_CUDA_CLEAN(cudaGetLastError());
+      SC_CUDA_CLEAN(cudaEventRecord(freed[which], stream));
+      up += uint64_t(cnt) * sizeof(double);
+    }
+  }
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
+
+  d->lgamma_sum = 0.0;
+  if (d->family == STAN_CUDA_POISSON_LOG && !d->y_is_double) {
+    const int nb = 256;
+    double* partial = nullptr;
+    SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&partial), nb * sizeof(double)));
+    lgamma_partial_kernel<<<nb, 256, 0, stream>>>(static_cast<const int*>(d->y), n, partial);
+    double host[256];
+    cudaError_t e = cudaMemcpyAsync(host, partial, sizeof(host), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(partial);
+    SC_CUDA_CLEAN(e);
+    double s = 0.0;
+    for (int i = 0; i < nb; ++i) s += host[i];
+    d->lgamma_sum = s;
+  }
+  SC_CUDA_CLEAN(cudaStreamSynchronize(stream));
+#undef SC_CUDA_CLEAN
+  cleanup();
+  if (bytes_uploaded) *bytes_uploaded = up;
+  return STAN_CUDA_OK;
+}
+
+int make_data_block(int device, int family, int64_t n_rows, int64_t k, const double* x, int64_t ldx,
+                    int x_row_major, const void* y, int y_is_double, int64_t row0, cudaStream_t stream,
+                    stan_cuda_data** out) {
+  if (n_rows <= 0 || k < 0 || !x || !y) return fail(STAN_CUDA_ERR_ARG, "data block: bad shape or null pointer");
+  if (family < 0 || family > 2) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
+  stan_cuda_data* d = new stan_cuda_data();
+  d->device = device;
+  d->family = family;
+  d->n = n_rows;
+  d->k = k;
+  d->y_is_double = y_is_double;
+  if (!choose_tiling(n_rows, k, 0, &d->t)) {
+    delete d;
+    return fail(STAN_CUDA_ERR_ARG, "data block: k > 512 is outside the fused kernel's range");
+  }
+  auto t0 = std::chrono::steady_clock::now();
+  uint64_t up = 0;
+  int rc = upload_glm_data(d, x, ldx, x_row_major, y, row0, stream, &up);
+  if (rc < 0) {
+    if (d->x) cudaFree(d->x);
+    if (d->y) cudaFree(d->y);
+    delete d;
+    return rc;
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  counters().bytes_uploaded.fetch_add(up);
+  counters().last_fill_ms.store(std::chrono::duration<double, std::milli>(t1 - t0).count());
+  *out = d;
+  return STAN_CUDA_OK;
+}
+
+void free_data_block(stan_cuda_data* d) {
+  if (!d) return;
+  cudaSetDevice(d->device);
+  if (d->x) cudaFree(d->x);
+  if (d->y) cudaFree(d->y);
+  workspace_free(&d->ws);
+  delete d;
+}
+
+}  // namespace stancuda
+
+using namespace stancuda;
+
+extern "C" {
+
+int stan_cuda_data_create(int family, int64_t n, int64_t k, const double* x, int64_t ldx, int x_row_major,
+                          const void* y, int y_is_double, stan_cuda_data_t* out) {
+  if (!out) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_data_create: null out");
+  SC_TRY(ensure_init());
+  int dev = 0;
+  SC_CUDA(cudaGetDevice(&dev));
+  // the caller's current device must be one of ours; default to the first
+  bool ok = false;
+  for (int d : context().devices) ok = ok || d == dev;
+  if (!ok) dev = context().devices[0];
+  ThreadDev* td;
+  SC_TRY(thread_dev(dev, &td));
+  return make_data_block(dev, family, n, k, x, ldx, x_row_major, y, y_is_double, 0, td->stream, out);
+}
+
+void stan_cuda_data_destroy(stan_cuda_data_t d) { free_data_block(d); }
+
+int64_t stan_cuda_data_params_len(stan_cuda_data_t d) { return d ? d->t.kpad + 2 : 0; }
+int64_t stan_cuda_data_result_len(stan_cuda_data_t d) { return d ? d->t.kpad + 4 : 0; }
+int64_t stan_cuda_data_kpad(stan_cuda_data_t d) { return d ? d->t.kpad : 0; }
+int64_t stan_cuda_data_algorithmic_bytes(stan_cuda_data_t d) {
+  if (!d) return 0;
+  return d->n * d->k * int64_t(sizeof(double)) + d->n * int64_t(d->y_is_double ? sizeof(double) : sizeof(int));
+}
+int stan_cuda_data_launches_per_eval(stan_cuda_data_t d) { return d ? 1 : 0; }
+
+int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params, const double* d_alpha_vec,
+                         const double* d_sigma_vec, double* d_result, double* d_row_dalpha,
+                         double* d_row_dsigma, void* stream) {
+  if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: null argument");
+  SC_CUDA(cudaSetDevice(d->device));
+  LaunchIO io{flags, d_params, d_alpha_vec, d_sigma_vec, d_result, d_row_dalpha, d_row_dsigma};
+  return launch_glm(d, io, &d->ws, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,519 @@
+// glm_fused.cu -- the fused GLM value+gradient kernel for sm_100a (FP64, HBM-bound).
+//
+// One pass over X computes, for a block of rows,
+//     eta = X*beta + alpha,  the per-row log-likelihood and d = dL/deta,  and  g = X^T d
+// i.e. the whole numeric body of
+//     bernoulli_logit_glm_lpmf  stan/math/prim/mat/prob/bernoulli_logit_glm_lpmf.hpp:88-135
+//     poisson_log_glm_lpmf      stan/math/prim/mat/prob/poisson_log_glm_lpmf.hpp:91-129
+//     normal_id_glm_lpdf        stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:100-172
+// which the reference does with two Eigen GEMVs (two reads of X) plus N-length temporaries, and
+// its OpenCL backend with two kernels (opencl/kernels/*_glm_*.hpp + row_vector_matrix_multiply,
+// opencl/kernels/matrix_multiply.hpp:354-386) and a round trip of d through global memory.
+//
+// Structure:
+//  * persistent CTAs, static round-robin tile schedule (deterministic sums);
+//  * a tile = R rows x kpad columns, contiguous in HBM, staged into shared memory by ONE 1-D TMA
+//    bulk copy (cp.async.bulk ... mbarrier::complete_tx) per tile into a ring of `stages` buffers;
+//  * thread (cg, r) pulls its 16 doubles of row r from shared memory into registers ONCE, uses
+//    them for the partial dot product (eta) and again for the gradient FMA after d is known:
+//    X crosses HBM once and shared memory once;
+//  * partial dots of the C column groups meet in shared memory, the row owner (cg == 0) runs the
+//    family epilogue, d goes back through shared memory;
+//  * per-thread gradient accumulators live in registers for the whole kernel; at the end a
+//    fixed-order warp-shuffle + block reduction writes one partial block per CTA, and the last
+//    CTA to finish (atomic ticket) adds the CTA partials in CTA order -> bit-reproducible.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace stancuda {
+
+struct GlmKernelParams {
+  const double* x;
+  const void* y;
+  int64_t n;          // valid rows
+  int tiles;
+  int R, C, kc, kpad;
+  int log2R;
+  int stages;
+  uint32_t stage_bytes;  // per stage in shared memory (tile + y, 128-aligned)
+  uint32_t tile_bytes;
+  uint32_t y_bytes;      // per tile
+  const double* params;
+  const double* alpha_vec;
+  const double* sigma_vec;
+  double* row_dalpha;
+  double* row_dsigma;
+  double* scratch;
+  unsigned int* ticket;
+  double* result;
+  uint32_t flags;
+  double lgamma_sum;
+};
+
+// ---------------------------------------------------------------------------------------------
+// PTX helpers: mbarrier + 1-D TMA bulk copy (SASS: UBLKCP / SYNCS)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
+                                             uint32_t bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1], %2, [%3], %4;" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// family epilogues: per-row log-likelihood terms and d = dL/deta, same expressions and the same
+// branch structure as the reference.
+// ---------------------------------------------------------------------------------------------
+struct RowTerms {
+  double d;   // derivative wrt the linear predictor
+  double t0;  // -> lp main term
+  double t2;  // normal: s^2
+};
+
+template <int FAMILY>
+__device__ __forceinline__ RowTerms row_epilogue(double eta, double alpha, double yv, double inv_sigma) {
+  RowTerms o;
+  if (FAMILY == STAN_CUDA_BERNOULLI_LOGIT) {
+    // bernoulli_logit_glm_lpmf.hpp:90-104,115-121 (cutoff = 20, the three-way select)
+    const double sign = 2.0 * yv - 1.0;
+    const double ytheta = sign * (eta + alpha);
+    const double e = exp(-ytheta);
+    o.t0 = ytheta > 20.0 ? -e : (ytheta < -20.0 ? ytheta : -log1p(e));
+    o.d = ytheta > 20.0 ? -e : (ytheta < -20.0 ? sign : sign * e / (e + 1.0));
+    o.t2 = 0.0;
+  } else if (FAMILY == STAN_CUDA_POISSON_LOG) {
+    // poisson_log_glm_lpmf.hpp:91-95,110-111
+    const double theta = eta + alpha;
+    const double e = exp(theta);
+    o.d = yv - e;
+    o.t0 = yv * theta - e;
+    o.t2 = 0.0;
+  } else {
+    // normal_id_glm_lpdf.hpp:108-117,138-141
+    const double s = (yv - eta - alpha) * inv_sigma;
+    o.d = inv_sigma * s;
+    o.t2 = s * s;
+    o.t0 = 0.0;
+  }
+  return o;
+}
+
+// Sum `v` over the `width` consecutive lanes that share a column group (width = min(R, 32)).
+__device__ __forceinline__ double group_reduce(double v, int width) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const double o = __shfl_xor_sync(0xffffffffu, v, off);
+    if (off < width) v += o;
+  }
+  return v;
+}
+
+template <int FAMILY, int THREADS, bool ROWIO>
+__global__ void __launch_bounds__(THREADS, (THREADS >= 512 ? 1 : (THREADS >= 256 ? 2 : 4)))
+glm_fused_kernel(const GlmKernelParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  constexpr int WARPS = THREADS / 32;
+  const int tid = threadIdx.x;
+  const int R = p.R, C = p.C, kc = p.kc, kpad = p.kpad;
+  const int r = tid & (R - 1);
+  const int cg = tid >> p.log2R;
+  const bool owner = cg == 0;
+  const bool multi = C > 1;
+
+  // ---- shared memory carve-up -------------------------------------------------------------
+  unsigned char* stage0 = smem;
+  double* part = reinterpret_cast<double*>(smem + size_t(p.stages) * p.stage_bytes);  // [THREADS]
+  double* dsm = part + THREADS;                                                       // [THREADS]
+  double* red = dsm + THREADS;                             // [2 * WARPS][kMaxKc + 4] leader slots
+  uint64_t* bars = reinterpret_cast<uint64_t*>(red + 2 * WARPS * (kMaxKc + 4));       // [stages]
+  __shared__ int s_is_last;
+
+  const int grid = gridDim.x;
+  const int ntl = (p.tiles - int(blockIdx.x) + grid - 1) / grid;  // tiles of this CTA
+  const uint32_t tx_bytes = p.tile_bytes + p.y_bytes;
+  const unsigned char* xbytes = reinterpret_cast<const unsigned char*>(p.x);
+  const unsigned char* ybytes = reinterpret_cast<const unsigned char*>(p.y);
+  uint64_t policy = 0;
+
+  auto issue = [&](int it) {  // thread 0 only: stage tile `it` of this CTA
+    const int s = it % p.stages;
+    const int64_t tile = int64_t(blockIdx.x) + int64_t(it) * grid;
+    const uint32_t bar = smem_u32(&bars[s]);
+    const uint32_t dst = smem_u32(stage0 + size_t(s) * p.stage_bytes);
+    mbar_expect_tx(bar, tx_bytes);
+    tma_bulk_g2s(dst, xbytes + tile * p.tile_bytes, p.tile_bytes, bar, policy);
+    tma_bulk_g2s(dst + p.tile_bytes, ybytes + tile * p.y_bytes, p.y_bytes, bar, policy);
+  };
+
+  if (tid == 0) {
+    for (int s = 0; s < p.stages; ++s) mbar_init(smem_u32(&bars[s]), 1);
+    mbar_fence_init();
+    policy = l2_evict_first_policy();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const int pre = ntl < p.stages ? ntl : p.stages;
+    for (int it = 0; it < pre; ++it) issue(it);
+  }
+
+  // ---- per-thread constants ---------------------------------------------------------------
+  double bj[kMaxKc], acc[kMaxKc];
+#pragma unroll
+  for (int j = 0; j < kMaxKc; ++j) {
+    bj[j] = j < kc ? p.params[cg * kc + j] : 0.0;
+    acc[j] = 0.0;
+  }
+  const double alpha0 = p.params[kpad];
+  const double sigma0 = p.params[kpad + 1];
+  const double inv_sigma0 = FAMILY == STAN_CUDA_NORMAL_ID ? 1.0 / sigma0 : 1.0;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // owner accumulators: lp main, sum d, sum s^2, sum log sigma
+
+  // ---- main loop over this CTA's tiles ------------------------------------------------------
+  for (int it = 0; it < ntl; ++it) {
+    const int s = it % p.stages;
+    const uint32_t parity = (it / p.stages) & 1;
+    const int64_t tile = int64_t(blockIdx.x) + int64_t(it) * grid;
+    const int64_t row = tile * R + r;
+    mbar_wait(smem_u32(&bars[s]), parity);
+
+    const unsigned char* st = stage0 + size_t(s) * p.stage_bytes;
+    const double* xs = reinterpret_cast<const double*>(st) + (cg * kc) * R + r;
+    double xr[kMaxKc];
+#pragma unroll
+    for (int j = 0; j < kMaxKc; ++j) xr[j] = j < kc ? xs[j * R] : 0.0;
+
+    double yv = 0.0, alpha = alpha0, inv_sigma = inv_sigma0, sigma_row = sigma0;
+    if (owner) {
+      if (FAMILY == STAN_CUDA_NORMAL_ID) {
+        yv = reinterpret_cast<const double*>(st + p.tile_bytes)[r];
+      } else {
+        yv = double(reinterpret_cast<const int*>(st + p.tile_bytes)[r]);
+      }
+      if (ROWIO && row < p.n) {
+        if (p.alpha_vec) alpha = p.alpha_vec[row];
+        if (FAMILY == STAN_CUDA_NORMAL_ID && p.sigma_vec) sigma_row = p.sigma_vec[row];
+      }
+    }
+
+    double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < kMaxKc; j += 2) {
+      p0 = fma(xr[j], bj[j], p0);
+      p1 = fma(xr[j + 1], bj[j + 1], p1);
+    }
+    double eta = p0 + p1;
+    if (multi) part[tid] = eta;
+    __syncthreads();  // every thread has drained stage s; partial dots are visible
+
+    if (tid == 0 && it + p.stages < ntl) issue(it + p.stages);
+
+    double d = 0.0;
+    if (owner) {
+      for (int c = 1; c < C; ++c) eta += part[c * R + r];  // fixed order over column groups
+      if (ROWIO && FAMILY == STAN_CUDA_NORMAL_ID && p.sigma_vec) inv_sigma = 1.0 / sigma_row;
+      RowTerms o = row_epilogue<FAMILY>(eta, alpha, yv, inv_sigma);
+      if (row < p.n) {
+        d = o.d;
+        a0 += o.t0;
+        a1 += o.d;
+        a2 += o.t2;
+        if (ROWIO) {
+          if (FAMILY == STAN_CUDA_NORMAL_ID && p.sigma_vec) {
+            a3 += log(sigma_row);
+            if (p.row_dsigma) p.row_dsigma[row] = (o.t2 - 1.0) * inv_sigma;
+          }
+          if (p.row_dalpha) p.row_dalpha[row] = o.d;
+        }
+      }
+      if (multi) dsm[r] = d;
+    }
+    if (multi) {
+      __syncthreads();
+      d = dsm[r];
+    }
+#pragma unroll
+    for (int j = 0; j < kMaxKc; ++j) acc[j] = fma(xr[j], d, acc[j]);
+  }
+
+  // ---- CTA reduction: lanes of a column group -> warps of a column group -> CTA partial -----
+  const int width = R < 32 ? R : 32;
+  const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int j = 0; j < kMaxKc; ++j) acc[j] = group_reduce(acc[j], width);
+  a0 = group_reduce(a0, width);
+  a1 = group_reduce(a1, width);
+  a2 = group_reduce(a2, width);
+  a3 = group_reduce(a3, width);
+  __syncthreads();
+  // slot (warp, sub) -> one leader lane per column group inside the warp
+  if ((lane & (width - 1)) == 0) {
+    // red is laid out [THREADS / width][kMaxKc + 4]
+    double* dst = red + size_t(tid / width) * (kMaxKc + 4);
+#pragma unroll
+    for (int j = 0; j < kMaxKc; ++j) dst[j] = acc[j];
+    dst[kMaxKc + 0] = a0;
+    dst[kMaxKc + 1] = a1;
+    dst[kMaxKc + 2] = a2;
+    dst[kMaxKc + 3] = a3;
+  }
+  __syncthreads();
+  const int cols = kpad + 4;
+  double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
+  const int slots_per_cg = R / width;  // leader slots per column group (>= 1)
+  for (int c = tid; c < cols; c += THREADS) {
+    double sum = 0.0;
+    if (c < 4) {  // scalars live in column group 0
+      for (int q = 0; q < slots_per_cg; ++q) sum += red[size_t(q) * (kMaxKc + 4) + kMaxKc + c];
+    } else {
+      const int col = c - 4, g = col / kc, j = col - g * kc;
+      const int first = g * slots_per_cg;  // leader slots are ordered by tid, i.e. by (cg, r)
+      for (int q = 0; q < slots_per_cg; ++q) sum += red[size_t(first + q) * (kMaxKc + 4) + j];
+    }
+    my_scratch[c] = sum;
+  }
+
+  // ---- last CTA adds the CTA partials in CTA order --------------------------------------------
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int t = atomicAdd(p.ticket, 1u);
+    s_is_last = (t == unsigned(grid) - 1u);
+  }
+  __syncthreads();
+  if (!s_is_last) return;
+  __threadfence();
+  for (int c = tid; c < cols; c += THREADS) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int b = 0;
+    for (; b + 4 <= grid; b += 4) {
+      s0 += __ldcg(p.scratch + size_t(b + 0) * cols + c);
+      s1 += __ldcg(p.scratch + size_t(b + 1) * cols + c);
+      s2 += __ldcg(p.scratch + size_t(b + 2) * cols + c);
+      s3 += __ldcg(p.scratch + size_t(b + 3) * cols + c);
+    }
+    for (; b < grid; ++b) s0 += __ldcg(p.scratch + size_t(b) * cols + c);
+    const double tot = (s0 + s1) + (s2 + s3);
+    if (c >= 4) p.result[c] = tot;
+    else part[c] = tot;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const double A0 = part[0], A1 = part[1], A2 = part[2], A3 = part[3];
+    const double nn = double(p.n);
+    double lp = 0.0, dsig = 0.0, witness;
+    if (FAMILY == STAN_CUDA_BERNOULLI_LOGIT) {
+      if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
+      witness = A0;  // bernoulli_logit_glm_lpmf.hpp:106 tests logp
+    } else if (FAMILY == STAN_CUDA_POISSON_LOG) {
+      if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;  // :102-108
+      if (p.flags & STAN_CUDA_LP_MAIN) lp += A0;             // :109-112
+      witness = A1;  // poisson_log_glm_lpmf.hpp:97 tests sum(theta_derivative)
+    } else {
+      // normal_id_glm_lpdf.hpp:159-172
+      const double NEG_LOG_SQRT_TWO_PI = -0.91893853320467274178032973640561763986;
+      if (p.flags & STAN_CUDA_LP_CONST) lp += NEG_LOG_SQRT_TWO_PI * nn;
+      if (p.flags & STAN_CUDA_LP_SCALE) lp -= p.sigma_vec ? A3 : nn * log(sigma0);
+      if (p.flags & STAN_CUDA_LP_MAIN) lp -= 0.5 * A2;
+      if (!p.sigma_vec) dsig = (A2 - nn) * inv_sigma0;  // :142-143
+      witness = A2;  // :150 tests y_scaled_sq_sum
+    }
+    p.result[0] = lp;
+    p.result[1] = A1;
+    p.result[2] = dsig;
+    p.result[3] = witness;
+    *p.ticket = 0u;  // ready for the next launch on this workspace (stream ordered)
+  }
+}
+
+}  // namespace stancuda
+
+// =============================================================================================
+// host side: tiling choice and launch
+// =============================================================================================
+namespace stancuda {
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  return atoi(v);
+}
+
+const Tuning& tuning() {
+  static Tuning t = [] {
+    Tuning u;
+    u.threads = env_int("STAN_CUDA_THREADS", 0);
+    u.stages = env_int("STAN_CUDA_STAGES", 0);
+    u.ctas_per_sm = env_int("STAN_CUDA_CTAS_PER_SM", 0);
+    return u;
+  }();
+  return t;
+}
+
+int sm_count(int device) {
+  static int cached[64] = {0};
+  if (device < 0 || device >= 64) return 148;
+  if (!cached[device]) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || v <= 0) v = 148;
+    cached[device] = v;
+  }
+  return cached[device];
+}
+
+bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t) {
+  int threads = threads_override ? threads_override : tuning().threads;
+  if (threads != 128 && threads != 256 && threads != 512) threads = 256;
+  if (k < 1) k = 1;
+  // smallest power-of-two number of column groups with at most kMaxKc columns per thread
+  int C = 1;
+  while ((k + C - 1) / C > kMaxKc) C *= 2;
+  while (threads / C < 16 && threads < 512) threads *= 2;  // keep >= 16 rows per tile
+  if (threads / C < 16) return false;                     // k > 512: outside the fused kernel
+  t->threads = threads;
+  t->C = C;
+  t->kc = int((k + C - 1) / C);
+  t->R = threads / C;
+  t->kpad = C * t->kc;
+  t->tiles = (n + t->R - 1) / t->R;
+  return true;
+}
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+template <int FAMILY, int THREADS, bool ROWIO>
+static int launch_inst(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
+  auto kern = glm_fused_kernel<FAMILY, THREADS, ROWIO>;
+  static std::atomic<size_t> configured[64];
+  int dev = 0;
+  SC_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && configured[dev].load(std::memory_order_relaxed) < smem) {
+    SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    configured[dev].store(smem, std::memory_order_relaxed);
+  }
+  kern<<<grid, THREADS, smem, stream>>>(p);
+  SC_CUDA(cudaGetLastError());
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
+  return STAN_CUDA_OK;
+}
+
+template <int FAMILY, bool ROWIO>
+static int launch_threads(int threads, const GlmKernelParams& p, int grid, size_t smem, cudaStream_t s) {
+  switch (threads) {
+    case 128: return launch_inst<FAMILY, 128, ROWIO>(p, grid, smem, s);
+    case 256: return launch_inst<FAMILY, 256, ROWIO>(p, grid, smem, s);
+    default: return launch_inst<FAMILY, 512, ROWIO>(p, grid, smem, s);
+  }
+}
+
+template <int FAMILY>
+static int launch_family(bool rowio, int threads, const GlmKernelParams& p, int grid, size_t smem,
+                         cudaStream_t s) {
+  return rowio ? launch_threads<FAMILY, true>(threads, p, grid, smem, s)
+               : launch_threads<FAMILY, false>(threads, p, grid, smem, s);
+}
+
+// Shared-memory footprint of one CTA with `stages` stages.
+static size_t smem_bytes(const Tiling& t, int stages, size_t* stage_bytes_out) {
+  const size_t stage = align_up(t.tile_bytes() + size_t(t.R) * sizeof(double), 128);
+  if (stage_bytes_out) *stage_bytes_out = stage;
+  const size_t fixed = (2 * size_t(t.threads) + 2 * size_t(t.threads / 32) * (kMaxKc + 4)) * sizeof(double)
+                       + size_t(stages) * sizeof(uint64_t);
+  return size_t(stages) * stage + fixed;
+}
+
+int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
+  const Tiling& t = d->t;
+  if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
+  const int sms = sm_count(d->device);
+  int ctas_per_sm = tuning().ctas_per_sm;
+  if (ctas_per_sm <= 0) ctas_per_sm = t.threads >= 512 ? 1 : (t.threads >= 256 ? 2 : 4);
+  // stages: as many as fit next to the other resident CTAs (228 KB per SM, 1 KB reserved per CTA)
+  const size_t budget = (size_t(228) * 1024) / ctas_per_sm - 1024 - 64;
+  int stages = tuning().stages;
+  size_t stage_bytes = 0;
+  if (stages <= 0) {
+    stages = 4;
+    while (stages > 1 && smem_bytes(t, stages, nullptr) > budget) --stages;
+  }
+  size_t smem = smem_bytes(t, stages, &stage_bytes);
+  while (stages > 1 && smem > size_t(227) * 1024) smem = smem_bytes(t, --stages, &stage_bytes);
+  if (smem > size_t(227) * 1024) return fail(STAN_CUDA_ERR_ARG, "launch_glm: tile does not fit shared memory");
+
+  int64_t grid64 = int64_t(sms) * ctas_per_sm;
+  if (grid64 > t.tiles) grid64 = t.tiles;
+  const int grid = int(grid64);
+  SC_TRY(workspace_reserve(ws, d->device, size_t(grid) * (t.kpad + 4)));
+
+  GlmKernelParams p;
+  p.x = d->x;
+  p.y = d->y;
+  p.n = d->n;
+  p.tiles = int(t.tiles);
+  p.R = t.R; p.C = t.C; p.kc = t.kc; p.kpad = t.kpad;
+  p.log2R = 0;
+  while ((1 << p.log2R) < t.R) ++p.log2R;
+  p.stages = stages;
+  p.stage_bytes = uint32_t(stage_bytes);
+  p.tile_bytes = uint32_t(t.tile_bytes());
+  p.y_bytes = uint32_t(size_t(t.R) * (d->y_is_double ? sizeof(double) : sizeof(int)));
+  p.params = io.d_params;
+  p.alpha_vec = io.d_alpha_vec;
+  p.sigma_vec = io.d_sigma_vec;
+  p.row_dalpha = io.d_row_dalpha;
+  p.row_dsigma = io.d_row_dsigma;
+  p.scratch = ws->scratch;
+  p.ticket = ws->ticket;
+  p.result = io.d_result;
+  p.flags = io.flags;
+  p.lgamma_sum = d->lgamma_sum;
+  const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
+  switch (d->family) {
+    case STAN_CUDA_BERNOULLI_LOGIT:
+      return launch_family<STAN_CUDA_BERNOULLI_LOGIT>(rowio, t.threads, p, grid, smem, stream);
+    case STAN_CUDA_POISSON_LOG:
+      return launch_family<STAN_CUDA_POISSON_LOG>(rowio, t.threads, p, grid, smem, stream);
+    case STAN_CUDA_NORMAL_ID:
+      return launch_family<STAN_CUDA_NORMAL_ID>(rowio, t.threads, p, grid, smem, stream);
+  }
+  return fail(STAN_CUDA_ERR_ARG, "launch_glm: unknown family");
+}
+
+}  // namespace stancuda

@@ -1,0 +1,301 @@
+"""Python mirrors of the reference's entry points over the C ABI (ctypes).
+
+Same names, argument order and error behaviour as the reference functions
+  bernoulli_logit_glm_lpmf(y, x, alpha, beta)     stan/math/prim/mat/prob/bernoulli_logit_glm_lpmf.hpp:46-49
+  poisson_log_glm_lpmf(y, x, alpha, beta)         stan/math/prim/mat/prob/poisson_log_glm_lpmf.hpp:44-49
+  normal_id_glm_lpdf(y, x, alpha, beta, sigma)    stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:49-53
+  normal_lpdf(y, mu, sigma)                       stan/math/prim/scal/prob/normal_lpdf.hpp:36-39
+Each returns (lp, grads) where grads holds what reverse mode would leave in the adjoints of the
+var arguments (alpha, beta, sigma, mu; y on request).  Size mismatches raise ValueError
+(std::invalid_argument), domain violations raise DomainError (std::domain_error).
+"""
+import contextlib
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from ._lib import StanCudaError, check, lib  # noqa: F401
+
+
+class DomainError(ValueError):
+    """Counterpart of std::domain_error thrown by the reference's check_* functions."""
+
+
+def init(n_devices=0):
+    check(lib().stan_cuda_init(n_devices))
+
+
+def init_device(ordinal):
+    check(lib().stan_cuda_init_device(ordinal))
+
+
+def describe():
+    return lib().stan_cuda_describe().decode()
+
+
+def stats():
+    s = _abi.Stats()
+    check(lib().stan_cuda_stats(C.byref(s)))
+    return {f: getattr(s, f) for f, _ in s._fields_}
+
+
+def cache_clear():
+    lib().stan_cuda_cache_clear()
+
+
+def cache_invalidate(arr):
+    return lib().stan_cuda_cache_invalidate(arr.ctypes.data)
+
+
+@contextlib.contextmanager
+def shard_scope(call_id, job, device):
+    """map_rect shard scope: evaluations inside run on `device`, data keyed by (call_id, job)."""
+    lib().stan_cuda_shard_scope_enter(call_id, job, device)
+    try:
+        yield
+    finally:
+        lib().stan_cuda_shard_scope_exit()
+
+
+def _f64(a):
+    return np.ascontiguousarray(np.atleast_1d(np.asarray(a, dtype=np.float64)))
+
+
+def _prep_x(x):
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim != 2:
+        raise ValueError("x must be a matrix")
+    if x.flags.f_contiguous:
+        return x, 0, max(x.shape[0], 1)
+    if x.flags.c_contiguous:
+        return x, 1, max(x.shape[1], 1)
+    x = np.asfortranarray(x)
+    return x, 0, max(x.shape[0], 1)
+
+
+def _size_check(function, name, v, n, other="Vector of dependent variables"):
+    # check_consistent_size(s): scalars are consistent with anything
+    if v.size != 1 and v.size != n:
+        raise ValueError("%s: %s has dimension = %d, expecting dimension = %d (%s)"
+                         % (function, name, v.size, n, other))
+
+
+def glm_flags(family, propto, alpha_var=True, beta_var=True, sigma_var=True, y_var=False):
+    """The include_summand<propto, ...> decisions of the three reference bodies, for the given
+    constness of the arguments (x is always data on this path)."""
+    any_var = alpha_var or beta_var or (family == _abi.NORMAL_ID and (sigma_var or y_var))
+    f = 0
+    if beta_var:
+        f |= _abi.NEED_DBETA
+    if alpha_var:
+        f |= _abi.NEED_DALPHA
+    if family == _abi.NORMAL_ID and sigma_var:
+        f |= _abi.NEED_DSIGMA
+    if family == _abi.NORMAL_ID and y_var:
+        f |= _abi.NEED_DY
+    if family == _abi.BERNOULLI_LOGIT:
+        f |= _abi.LP_MAIN                      # bernoulli_logit_glm_lpmf.hpp:101-104 (no summand test)
+    elif family == _abi.POISSON_LOG:
+        if not propto:                         # poisson_log_glm_lpmf.hpp:102,109: both tests reduce to !propto
+            f |= _abi.LP_CONST | _abi.LP_MAIN
+    else:
+        if not propto:
+            f |= _abi.LP_CONST                 # normal_id_glm_lpdf.hpp:160
+        if not propto or sigma_var:
+            f |= _abi.LP_SCALE                 # :163
+        if not propto or any_var:
+            f |= _abi.LP_MAIN                  # :170
+    return f
+
+
+def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, need_dy=False):
+    """Raw C-ABI call (no argument checks beyond shapes).  Returns dict with rc, lp and partials."""
+    fam = _abi.FAMILIES[family] if isinstance(family, str) else family
+    x, row_major, ldx = _prep_x(x)
+    n, k = x.shape
+    if fam == _abi.NORMAL_ID:
+        y = _f64(y)
+    else:
+        y = np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+    if y.size == 1 and n != 1:
+        y = np.full(n, y[0], dtype=y.dtype)
+    alpha, beta = _f64(alpha), _f64(beta)
+    sigma = _f64(sigma) if sigma is not None else None
+    if flags is None:
+        flags = glm_flags(fam, propto, y_var=need_dy)
+    a = _abi.GlmArgs()
+    lp, dbeta, dalpha = np.zeros(1), np.zeros(max(k, 1)), np.zeros(max(alpha.size, 1))
+    dsigma = np.zeros(max(sigma.size, 1)) if sigma is not None else np.zeros(1)
+    dy = np.zeros(max(n, 1)) if (flags & _abi.NEED_DY) else None
+    aux = np.zeros(4)
+    a.family, a.flags, a.n, a.k = fam, flags, n, k
+    a.x, a.ldx, a.x_row_major = x.ctypes.data, ldx, row_major
+    a.y, a.y_is_double = y.ctypes.data, int(fam == _abi.NORMAL_ID)
+    a.alpha, a.alpha_len, a.beta = alpha.ctypes.data, alpha.size, beta.ctypes.data
+    if sigma is not None:
+        a.sigma, a.sigma_len = sigma.ctypes.data, sigma.size
+    a.lp, a.dbeta, a.dalpha, a.dsigma = lp.ctypes.data, dbeta.ctypes.data, dalpha.ctypes.data, dsigma.ctypes.data
+    a.dy = dy.ctypes.data if dy is not None else None
+    a.aux = aux.ctypes.data
+    rc = check(lib().stan_cuda_glm_eval(C.byref(a)))
+    out = {"rc": rc, "lp": float(lp[0]), "dbeta": dbeta[:k].copy(), "dalpha": dalpha[:alpha.size].copy(),
+           "aux": aux, "_keep": (x, y)}
+    if fam == _abi.NORMAL_ID:
+        out["dsigma"] = dsigma[:sigma.size].copy()
+    if dy is not None:
+        out["dy"] = dy[:n].copy()
+    return out
+
+
+def _lazy_finite_checks(function, fam, rc, x, y, alpha, beta, sigma):
+    """The reference's lazy check_finite sequence, run only when the result is not finite
+    (bernoulli_logit_glm_lpmf.hpp:106-110, poisson_log_glm_lpmf.hpp:97-101,
+    normal_id_glm_lpdf.hpp:150-156).  Quirk kept on purpose: for bernoulli and poisson the last
+    check is handed an Eigen::Array, which check_finite treats as ONE element (is_vector<Array> is
+    false), so only row 0 of the linear predictor is looked at; if that row is finite the
+    reference returns the non-finite value without throwing -- and so does this wrapper."""
+    if rc != _abi.NONFINITE:
+        return
+    if fam == _abi.NORMAL_ID and not np.all(np.isfinite(y)):
+        raise DomainError("%s: Vector of dependent variables is not finite" % function)
+    if not np.all(np.isfinite(beta)):
+        raise DomainError("%s: Weight vector is not finite" % function)
+    if not np.all(np.isfinite(alpha)):
+        raise DomainError("%s: Intercept is not finite" % function)
+    if fam == _abi.NORMAL_ID:
+        raise DomainError("%s: Matrix of independent variables is not finite" % function)
+    with np.errstate(all="ignore"):
+        theta0 = float(np.dot(x[0, :], np.broadcast_to(beta, (x.shape[1],))) + alpha[0])
+    if not np.isfinite(theta0):
+        raise DomainError("%s: Matrix of independent variables[1] is not finite" % function)
+
+
+def _glm(function, fam, y, x, alpha, beta, sigma, propto, need_dy=False):
+    xa = np.asarray(x, dtype=np.float64)
+    if xa.ndim != 2:
+        raise ValueError("%s: x must be a matrix" % function)
+    n, k = xa.shape
+    ya = np.atleast_1d(np.asarray(y))
+    al, be = _f64(alpha), _f64(beta)
+    sg = _f64(sigma) if sigma is not None else None
+    if fam == _abi.NORMAL_ID:
+        if not (np.all(np.isfinite(sg)) and np.all(sg > 0)):       # check_positive_finite, :70
+            raise DomainError("%s: Scale vector must be positive finite" % function)
+    _size_check(function, "Vector of dependent variables", ya, n)
+    if be.size != k and not (be.size == 1 and k == 1):
+        raise ValueError("%s: Weight vector has dimension = %d, expecting dimension = %d" % (function, be.size, k))
+    if sg is not None:
+        _size_check(function, "Vector of scale parameters", sg, n)
+    _size_check(function, "Vector of intercepts", al, n)
+    if fam == _abi.BERNOULLI_LOGIT and ya.size and not np.all((ya >= 0) & (ya <= 1)):   # check_bounded, :70
+        raise DomainError("%s: Vector of dependent variables must be in the interval [0, 1]" % function)
+    if fam == _abi.POISSON_LOG and ya.size and not np.all(ya >= 0):                     # check_nonnegative, :70
+        raise DomainError("%s: Vector of dependent variables must be >= 0" % function)
+    if n == 0 or (fam == _abi.NORMAL_ID and sg.size == 0):
+        return 0.0, {}
+    r = glm_eval(fam, ya, xa, al, be, sg, propto=propto, need_dy=need_dy)
+    _lazy_finite_checks(function, fam, r["rc"], xa, ya, al, be, sg)
+    grads = {"beta": r["dbeta"], "alpha": r["dalpha"]}
+    if fam == _abi.NORMAL_ID:
+        grads["sigma"] = r["dsigma"]
+    if need_dy:
+        grads["y"] = r["dy"]
+    return r["lp"], grads
+
+
+def bernoulli_logit_glm_lpmf(y, x, alpha, beta, propto=False):
+    return _glm("bernoulli_logit_glm_lpmf", _abi.BERNOULLI_LOGIT, y, x, alpha, beta, None, propto)
+
+
+def poisson_log_glm_lpmf(y, x, alpha, beta, propto=False):
+    return _glm("poisson_log_glm_lpmf", _abi.POISSON_LOG, y, x, alpha, beta, None, propto)
+
+
+def normal_id_glm_lpdf(y, x, alpha, beta, sigma, propto=False, need_dy=False):
+    return _glm("normal_id_glm_lpdf", _abi.NORMAL_ID, y, x, alpha, beta, sigma, propto, need_dy)
+
+
+def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
+    """normal_lpdf(y | mu, sigma) with mu and sigma as the differentiated operands."""
+    function = "normal_lpdf"
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    if min(y.size, mu.size, sigma.size) == 0:
+        return 0.0, {}
+    if np.any(np.isnan(y)):
+        raise DomainError("%s: Random variable is nan" % function)          # check_not_nan, :51
+    if not np.all(np.isfinite(mu)):
+        raise DomainError("%s: Location parameter must be finite" % function)  # check_finite, :52
+    if not np.all(sigma > 0):
+        raise DomainError("%s: Scale parameter must be > 0" % function)      # check_positive, :53
+    n = max(y.size, mu.size, sigma.size)
+    for name, v in (("Random variable", y), ("Location parameter", mu), ("Scale parameter", sigma)):
+        if v.size != 1 and v.size != n:
+            raise ValueError("%s: %s has dimension = %d, expecting dimension = %d" % (function, name, v.size, n))
+    flags = _abi.NEED_DALPHA | _abi.NEED_DSIGMA | (_abi.NEED_DY if need_dy else 0)
+    flags |= (_abi.LP_SCALE | _abi.LP_MAIN) if propto else _abi.LP_ALL
+    a = _abi.NormalArgs()
+    lp, dmu, dsigma, dy = np.zeros(1), np.zeros(mu.size), np.zeros(sigma.size), np.zeros(y.size)
+    a.flags, a.y_is_data, a.n = flags, int(y_is_data), n
+    a.y, a.y_len, a.mu, a.mu_len = y.ctypes.data, y.size, mu.ctypes.data, mu.size
+    a.sigma, a.sigma_len = sigma.ctypes.data, sigma.size
+    a.lp, a.dmu, a.dsigma, a.dy = lp.ctypes.data, dmu.ctypes.data, dsigma.ctypes.data, dy.ctypes.data
+    check(lib().stan_cuda_normal_lpdf_eval(C.byref(a)))
+    grads = {"mu": dmu, "sigma": dsigma}
+    if need_dy:
+        grads["y"] = dy
+    return float(lp[0]), grads
+
+
+class GlmData:
+    """Device-resident (x, y) of one GLM: the explicit form of the cache fill, for callers that
+    own streams and device buffers themselves (bench.py via torch)."""
+
+    def __init__(self, family, x, y):
+        fam = _abi.FAMILIES[family] if isinstance(family, str) else family
+        x, row_major, ldx = _prep_x(x)
+        if fam == _abi.NORMAL_ID:
+            y = _f64(y)
+        else:
+            y = np.ascontiguousarray(np.asarray(y, dtype=np.int32))
+        n, k = x.shape
+        h = C.c_void_p()
+        check(lib().stan_cuda_data_create(fam, n, k, x.ctypes.data, ldx, row_major, y.ctypes.data,
+                                          int(fam == _abi.NORMAL_ID), C.byref(h)))
+        self.h, self.family, self.n, self.k = h, fam, n, k
+        self.kpad = lib().stan_cuda_data_kpad(h)
+        self.params_len = lib().stan_cuda_data_params_len(h)
+        self.result_len = lib().stan_cuda_data_result_len(h)
+        self.algorithmic_bytes = lib().stan_cuda_data_algorithmic_bytes(h)
+        self.launches_per_eval = lib().stan_cuda_data_launches_per_eval(h)
+
+    def launch(self, flags, d_params, d_result, stream, d_alpha_vec=None, d_sigma_vec=None,
+               d_row_dalpha=None, d_row_dsigma=None):
+        """Enqueue one fused evaluation; all pointers are device addresses (ints)."""
+        check(lib().stan_cuda_glm_launch(self.h, flags, d_params, d_alpha_vec, d_sigma_vec, d_result,
+                                         d_row_dalpha, d_row_dsigma, stream))
+
+    def close(self):
+        if self.h:
+            lib().stan_cuda_data_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def comm_init_from_torch(dist):
+    """Build the library's NCCL communicator over an initialised torch.distributed group: rank 0
+    creates the unique id, torch carries the 128 bytes to the other ranks (plumbing only)."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if world == 1:
+        return
+    buf = C.create_string_buffer(128)
+    if rank == 0:
+        check(lib().stan_cuda_comm_unique_id(buf))
+    box = [bytes(buf.raw)]
+    dist.broadcast_object_list(box, src=0)
+    check(lib().stan_cuda_comm_init_rank(world, rank, box[0]))

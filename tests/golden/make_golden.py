@@ -1,0 +1,118 @@
+"""Generates tests/golden/glm_golden.npz from the COMPILED REFERENCE (oracle/_ref/libstanref.so).
+
+Run in the dev container (needs /root/reference to have built the shim):
+    python tests/golden/make_golden.py
+Cases:
+  * the fixed fixtures of the reference's own GLM unit tests
+    (test/unit/math/rev/mat/prob/{bernoulli_logit,poisson_log,normal_id}_glm_*_test.cpp)
+  * the extreme-value bernoulli fixture exercising the cutoff branches (bernoulli..._test.cpp:63-108)
+  * vector-alpha / vector-sigma / var-y variants, propto on and off
+  * a 153 x 71 random case per family (the size of the reference's OpenCL-vs-CPU "big" test,
+    test/unit/math/opencl/rev/bernoulli_logit_glm_lpmf_test.cpp:255-297) and a 2000 x 128 one
+  * normal_lpdf: the reference's known-answer triples (test/prob/normal/normal_test.hpp:11-40)
+    plus a vectorised case
+Every case stores inputs and the reference's outputs (value + all adjoints).
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import loader as L  # noqa: E402
+
+out = {}
+names = []
+
+
+def add_glm(name, fam, x, y, alpha, beta, sigma=None, propto=False, need_dy=False, xkey=None):
+    r = L.ref_glm(fam, x, y, alpha, beta, sigma, propto=propto, need_dy=need_dy)
+    p = "glm/%s/" % name
+    xkey = xkey or name
+    out[p + "xkey"] = np.array(xkey)   # design matrices are stored once and shared between cases
+    out[p + "family"] = np.array(L._abi.FAMILIES[fam])
+    out[p + "propto"] = np.array(int(propto))
+    out[p + "need_dy"] = np.array(int(need_dy))
+    out["x/" + xkey] = np.asarray(x, float)
+    out[p + "y"] = np.asarray(y, float if fam == "normal_id" else np.int32)
+    out[p + "alpha"] = np.atleast_1d(np.asarray(alpha, float))
+    out[p + "beta"] = np.atleast_1d(np.asarray(beta, float))
+    if sigma is not None:
+        out[p + "sigma"] = np.atleast_1d(np.asarray(sigma, float))
+    out[p + "lp"] = np.array(r["lp"])
+    out[p + "dbeta"] = r["dbeta"]
+    out[p + "dalpha"] = r["dalpha"]
+    if "dsigma" in r:
+        out[p + "dsigma"] = r["dsigma"]
+    if need_dy:
+        out[p + "dy"] = r["dy"]
+    names.append("glm/" + name)
+
+
+X = np.array([[-12, 46], [-42, 24], [25, 27]], float)
+BETA, ALPHA = [0.3, 2.0], 0.3
+for propto in (False, True):
+    s = "_propto" if propto else ""
+    add_glm("bern_fixture" + s, "bernoulli_logit", X, [1, 0, 1], ALPHA, BETA, propto=propto)
+    add_glm("bern_fixture2" + s, "bernoulli_logit", X, [0, 1, 0], ALPHA, BETA, propto=propto)
+    add_glm("pois_fixture" + s, "poisson_log", X * 0.01, [15, 3, 5], ALPHA, BETA, propto=propto)
+    add_glm("pois_fixture2" + s, "poisson_log", X * 0.01, [14, 2, 5], ALPHA, BETA, propto=propto)
+    add_glm("norm_fixture" + s, "normal_id", X, [51., 32., 12.], ALPHA, BETA, [10.0], propto=propto)
+    add_glm("norm_fixture2" + s, "normal_id", X, [14., 32., 21.], ALPHA, BETA, [10.0], propto=propto)
+# cutoff branches: |ytheta| > 20 on both sides
+Xe = np.array([[-1234, 46], [-42, 24], [25, 27]], float)
+add_glm("bern_extreme", "bernoulli_logit", Xe, [1, 0, 1], 0.3, [0.3, 2000.0])
+add_glm("bern_extreme2", "bernoulli_logit", Xe, [0, 1, 0], 0.3, [0.3, 2000.0])
+
+rng = np.random.default_rng(20191104)
+for n, k, tag in ((153, 71, "big"), (600, 128, "wide"), (1000, 1, "k1"), (37, 16, "k16"), (300, 300, "k300")):
+    x = rng.standard_normal((n, k))
+    bt = rng.standard_normal(k) * (0.6 / np.sqrt(k))
+    beta = bt + rng.standard_normal(k) * 0.05
+    eta = 0.2 + x @ bt
+    add_glm("bern_" + tag, "bernoulli_logit", x, (rng.random(n) < 1 / (1 + np.exp(-eta))).astype(np.int32), 0.3, beta, xkey=tag)
+    add_glm("pois_" + tag, "poisson_log", x, rng.poisson(np.exp(eta)), 0.3, beta, xkey=tag)
+    yn = eta + 0.7 * rng.standard_normal(n)
+    add_glm("norm_" + tag, "normal_id", x, yn, 0.3, beta, [1.0], xkey=tag)
+    if tag == "big":
+        av = 0.3 + 0.1 * rng.standard_normal(n)
+        sv = 0.5 + rng.random(n)
+        add_glm("bern_big_valpha", "bernoulli_logit", x, (rng.random(n) < 0.5).astype(np.int32), av, beta, xkey=tag)
+        add_glm("pois_big_valpha", "poisson_log", x, rng.poisson(np.exp(eta)), av, beta, xkey=tag)
+        add_glm("norm_big_valpha_vsigma", "normal_id", x, yn, av, beta, sv, xkey=tag)
+        add_glm("norm_big_vsigma_dy", "normal_id", x, yn, 0.3, beta, sv, need_dy=True, xkey=tag)
+        add_glm("norm_big_dy_propto", "normal_id", x, yn, av, beta, [1.3], propto=True, need_dy=True, xkey=tag)
+
+nl = []
+
+
+def add_normal(name, y, mu, sigma, propto=False, need_dy=False, value_only=None):
+    p = "normal/%s/" % name
+    r = L.ref_normal_lpdf(y, mu, sigma, propto=propto, need_dy=need_dy)
+    out[p + "y"], out[p + "mu"], out[p + "sigma"] = (np.atleast_1d(np.asarray(v, float)) for v in (y, mu, sigma))
+    out[p + "propto"], out[p + "need_dy"] = np.array(int(propto)), np.array(int(need_dy))
+    out[p + "lp"], out[p + "dmu"], out[p + "dsigma"] = np.array(r["lp"]), r["dmu"], r["dsigma"]
+    if need_dy:
+        out[p + "dy"] = r["dy"]
+    if value_only is not None:
+        out[p + "known_answer"] = np.array(value_only)  # literal from the reference's test file
+    nl.append("normal/" + name)
+
+
+# test/prob/normal/normal_test.hpp:11-40 (literal expected log-densities)
+add_normal("ka0", [0.0], [0.0], [1.0], value_only=-0.918938533204672669541)
+add_normal("ka1", [1.0], [0.0], [1.0], value_only=-1.418938533204672669541)
+add_normal("ka2", [-2.0], [0.0], [1.0], value_only=-2.918938533204672669541)
+add_normal("ka3", [-3.5], [1.9], [7.2], value_only=-3.174269559226682080322)
+yv = rng.standard_normal(1000)
+add_normal("vec_mu", yv, 0.1 * rng.standard_normal(1000), [1.3])
+add_normal("vec_mu_propto", yv, 0.1 * rng.standard_normal(1000), [1.3], propto=True)
+add_normal("vec_all_dy", yv, 0.1 * rng.standard_normal(1000), 0.5 + rng.random(1000), need_dy=True)
+add_normal("scalar_mu", yv, [0.25], [0.8])
+
+out["glm_cases"] = np.array(names)
+out["normal_cases"] = np.array(nl)
+path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "glm_golden.npz")
+np.savez_compressed(path, **out)
+print("wrote", path, len(names), "GLM cases,", len(nl), "normal cases,", os.path.getsize(path), "bytes")

@@ -1,0 +1,77 @@
+"""Shared helpers of the test-suite: golden-case access, the parity metric, synthetic inputs."""
+import numpy as np
+
+from math_b200 import _abi
+
+RTOL = 1e-10  # north star: 1e-10 relative on the log-density and every gradient component
+
+
+def rel_err(got, ref):
+    """SURVEY 8(d) parity gate: |d| / max(|ref|, 1e-6 * ||ref||_inf), worst component."""
+    got, ref = np.atleast_1d(np.asarray(got, float)), np.atleast_1d(np.asarray(ref, float))
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    if ref.size == 0:
+        return 0.0
+    scale = np.maximum(np.abs(ref), 1e-6 * np.max(np.abs(ref)))
+    scale = np.where(scale == 0, 1.0, scale)
+    return float(np.max(np.abs(got - ref) / scale))
+
+
+def assert_close(got, ref, what, rtol=RTOL):
+    e = rel_err(got, ref)
+    assert e <= rtol, "%s: rel err %.3e > %.1e" % (what, e, rtol)
+
+
+def glm_case(golden, name):
+    p = name + "/"
+    fam = int(golden[p + "family"])
+    c = {"family": fam, "propto": bool(golden[p + "propto"]), "need_dy": bool(golden[p + "need_dy"]),
+         "x": golden["x/" + str(golden[p + "xkey"])], "y": golden[p + "y"], "alpha": golden[p + "alpha"],
+         "beta": golden[p + "beta"], "sigma": golden[p + "sigma"] if fam == _abi.NORMAL_ID else None,
+         "lp": float(golden[p + "lp"]), "dbeta": golden[p + "dbeta"], "dalpha": golden[p + "dalpha"]}
+    if fam == _abi.NORMAL_ID:
+        c["dsigma"] = golden[p + "dsigma"]
+    if c["need_dy"]:
+        c["dy"] = golden[p + "dy"]
+    return c
+
+
+def normal_case(golden, name):
+    p = name + "/"
+    c = {k: golden[p + k] for k in ("y", "mu", "sigma", "dmu", "dsigma")}
+    c["propto"], c["need_dy"], c["lp"] = bool(golden[p + "propto"]), bool(golden[p + "need_dy"]), float(golden[p + "lp"])
+    if c["need_dy"]:
+        c["dy"] = golden[p + "dy"]
+    if p + "known_answer" in golden.files:
+        c["known_answer"] = float(golden[p + "known_answer"])
+    return c
+
+
+def check_glm_result(r, c, what, rtol=RTOL):
+    assert_close(r["lp"], c["lp"], what + " lp", rtol)
+    assert_close(r["dbeta"], c["dbeta"], what + " dbeta", rtol)
+    assert_close(r["dalpha"], c["dalpha"], what + " dalpha", rtol)
+    if "dsigma" in c:
+        assert_close(r["dsigma"], c["dsigma"], what + " dsigma", rtol)
+    if "dy" in c:
+        assert_close(r["dy"], c["dy"], what + " dy", rtol)
+
+
+def synth_glm(family, n, k, seed, dtype_y=None):
+    """Synthetic inputs of SURVEY 8(d): X ~ N(0,1); y drawn from the model at (alpha_true,
+    beta_true); evaluation point perturbed away from the truth so no gradient cancels."""
+    fam = _abi.FAMILIES[family] if isinstance(family, str) else family
+    rng = np.random.default_rng(seed)
+    x = np.asfortranarray(rng.standard_normal((n, k)))
+    sd = 0.1 if k <= 32 else 0.05
+    beta_true = rng.standard_normal(k) * sd
+    eta = 0.2 + x @ beta_true
+    if fam == _abi.BERNOULLI_LOGIT:
+        y = (rng.random(n) < 1.0 / (1.0 + np.exp(-eta))).astype(np.int32)
+    elif fam == _abi.POISSON_LOG:
+        y = rng.poisson(np.exp(eta)).astype(np.int32)
+    else:
+        y = eta + 0.7 * rng.standard_normal(n)
+    beta = beta_true + 0.02 * rng.standard_normal(k)
+    return {"family": fam, "x": x, "y": y, "alpha": np.array([0.3]), "beta": beta,
+            "sigma": np.array([1.0]) if fam == _abi.NORMAL_ID else None}

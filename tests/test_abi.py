@@ -1,0 +1,94 @@
+"""CPU tests (no GPU): the C-ABI library builds, loads and exports exactly what include/stan_cuda.h
+declares; argument validation that needs no device; loud failure without a GPU."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from math_b200 import _abi
+from math_b200.build import LIB, build
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    text = open(os.path.join(ROOT, "include", "stan_cuda.h")).read()
+    return sorted(set(re.findall(r"STAN_CUDA_API\s+[\w\s\*]+?\b(stan_cuda_\w+)\s*\(", text)))
+
+
+@pytest.fixture(scope="module")
+def cdll():
+    build()
+    return ctypes.CDLL(LIB)
+
+
+def test_header_and_ctypes_mirror_agree():
+    assert declared_functions() == sorted(_abi.PROTOTYPES)
+
+
+def test_library_exports_every_declared_symbol(cdll):
+    for name in declared_functions():
+        assert hasattr(cdll, name), name
+    _abi.bind(cdll)
+
+
+def test_struct_layout_matches_header(cdll):
+    # sizes implied by the header's field order on LP64
+    assert ctypes.sizeof(_abi.GlmArgs) == 4 + 4 + 8 + 8 + 8 + 8 + 4 + 4 + 8 * 12
+    assert ctypes.sizeof(_abi.NormalArgs) == 4 + 4 + 8 * 11
+    assert ctypes.sizeof(_abi.Stats) == 8 * 7
+
+
+def test_argument_validation_needs_no_device(cdll):
+    lib = _abi.bind(cdll)
+    assert lib.stan_cuda_glm_eval(None) == _abi.ERR_ARG
+    a = _abi.GlmArgs()
+    a.family, a.n, a.k = 7, 3, 2
+    assert lib.stan_cuda_glm_eval(ctypes.byref(a)) == _abi.ERR_ARG
+    assert b"family" in lib.stan_cuda_last_error()
+    # n == 0 returns 0 like size_zero(y) in the reference, before any device work
+    lp = np.full(1, 5.0)
+    al = np.zeros(1)
+    a = _abi.GlmArgs()
+    a.family, a.n, a.k, a.alpha, a.alpha_len, a.lp = 1, 0, 0, al.ctypes.data, 1, lp.ctypes.data
+    assert lib.stan_cuda_glm_eval(ctypes.byref(a)) == 0 and lp[0] == 0.0
+
+
+def test_fails_loudly_without_gpu(cdll):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = _abi.bind(cdll)
+    assert lib.stan_cuda_init(0) == _abi.ERR_CUDA
+    assert b"no CPU fallback" in lib.stan_cuda_last_error()
+    from math_b200 import glm
+    with pytest.raises(glm.StanCudaError):
+        glm.poisson_log_glm_lpmf([1, 2], np.ones((2, 2)), 0.1, [0.1, 0.2])
+
+
+def test_host_wrapper_error_contract_without_device():
+    """Eager checks run before the ABI call, exactly where the reference has them."""
+    from math_b200 import glm
+    x = np.ones((3, 2))
+    with pytest.raises(glm.DomainError):
+        glm.bernoulli_logit_glm_lpmf([1, 0, 23], x, 0.3, [0.1, 0.2])
+    with pytest.raises(glm.DomainError):
+        glm.poisson_log_glm_lpmf([1, 0, -1], x, 0.3, [0.1, 0.2])
+    with pytest.raises(glm.DomainError):
+        glm.normal_id_glm_lpdf([1.0, 0.0, 2.0], x, 0.3, [0.1, 0.2], [0.0])
+    with pytest.raises(ValueError):
+        glm.poisson_log_glm_lpmf([1, 0], x, 0.3, [0.1, 0.2])
+    with pytest.raises(ValueError):
+        glm.poisson_log_glm_lpmf([1, 0, 2], x, 0.3, [0.1, 0.2, 0.3])
+    with pytest.raises(ValueError):
+        glm.poisson_log_glm_lpmf([1, 0, 2], x, [0.3, 0.1], [0.1, 0.2])
+    assert glm.poisson_log_glm_lpmf(np.zeros(0, int), np.zeros((0, 2)), 0.3, [0.1, 0.2])[0] == 0.0
+    with pytest.raises(glm.DomainError):
+        glm.normal_lpdf([np.nan], [0.0], [1.0])
+    with pytest.raises(glm.DomainError):
+        glm.normal_lpdf([0.0], [np.inf], [1.0])
+    with pytest.raises(glm.DomainError):
+        glm.normal_lpdf([0.0], [0.0], [0.0])
+    assert glm.normal_lpdf([], [0.0], [1.0])[0] == 0.0

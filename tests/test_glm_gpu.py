@@ -1,0 +1,251 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI, against
+the golden vectors produced by the reference and against the plain-C oracle on seeded inputs.
+Bar: 1e-10 relative on the log-density and on every gradient component (tests/helpers.rel_err)."""
+import numpy as np
+import pytest
+
+from math_b200 import _abi
+from tests.helpers import RTOL, assert_close, check_glm_result, glm_case, normal_case, synth_glm
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def glm():
+    from math_b200 import glm as g
+    g.init(1)
+    return g
+
+
+@pytest.fixture(scope="module")
+def L():
+    from oracle import loader
+    return loader
+
+
+def run_case(glm, c, **kw):
+    return glm.glm_eval(c["family"], c["y"], c["x"], c["alpha"], c["beta"], c["sigma"],
+                        propto=c.get("propto", False), need_dy=c.get("need_dy", False), **kw)
+
+
+def test_library_reports_b200(glm):
+    d = glm.describe()
+    assert "sm_100" in d or "sm_103" in d, d
+
+
+def test_golden_glm_cases(glm, golden):
+    for name in golden["glm_cases"]:
+        c = glm_case(golden, str(name))
+        r = run_case(glm, c)
+        assert r["rc"] == 0, name
+        check_glm_result(r, c, "cuda vs golden " + str(name))
+
+
+def test_golden_normal_cases(glm, golden):
+    for name in golden["normal_cases"]:
+        c = normal_case(golden, str(name))
+        lp, g = glm.normal_lpdf(c["y"], c["mu"], c["sigma"], propto=c["propto"], need_dy=c["need_dy"])
+        assert_close(lp, c["lp"], str(name) + " lp")
+        assert_close(g["mu"], c["dmu"], str(name) + " dmu")
+        assert_close(g["sigma"], c["dsigma"], str(name) + " dsigma")
+        if c["need_dy"]:
+            assert_close(g["y"], c["dy"], str(name) + " dy")
+        if "known_answer" in c:
+            assert abs(lp - c["known_answer"]) <= 1e-14 * max(1.0, abs(c["known_answer"]))
+
+
+SHAPES = [(1, 1), (5, 2), (33, 7), (1000, 16), (4097, 33), (100000, 32), (30011, 128), (9000, 256), (2100, 500),
+          (777, 100)]
+
+
+@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id"])
+@pytest.mark.parametrize("n,k", SHAPES)
+def test_against_oracle(glm, L, family, n, k):
+    s = synth_glm(family, n, k, seed=7 * n + k)
+    for propto in (False, True):
+        ref = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"], propto=propto)
+        got = glm.glm_eval(family, s["y"], s["x"], s["alpha"], s["beta"], s["sigma"], propto=propto)
+        assert got["rc"] == ref["rc"] == 0
+        check_glm_result(got, ref, "%s %dx%d propto=%s" % (family, n, k, propto))
+
+
+@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id"])
+def test_vector_alpha_sigma_and_dy(glm, L, family):
+    n, k = 5003, 40
+    s = synth_glm(family, n, k, seed=99)
+    rng = np.random.default_rng(3)
+    alpha = 0.3 + 0.1 * rng.standard_normal(n)
+    sigma = 0.5 + rng.random(n) if family == "normal_id" else None
+    need_dy = family == "normal_id"
+    ref = L.oracle_glm(family, s["x"], s["y"], alpha, s["beta"], sigma, need_dy=need_dy)
+    got = glm.glm_eval(family, s["y"], s["x"], alpha, s["beta"], sigma, need_dy=need_dy)
+    check_glm_result(got, ref, family + " vector alpha/sigma")
+    if need_dy:
+        assert_close(got["dy"], ref["dy"], "dy")
+
+
+def test_row_major_x_and_leading_dimension(glm, L):
+    s = synth_glm("poisson_log", 3001, 19, seed=11)
+    ref = L.oracle_glm("poisson_log", s["x"], s["y"], s["alpha"], s["beta"])
+    got = glm.glm_eval("poisson_log", s["y"], np.ascontiguousarray(s["x"]), s["alpha"], s["beta"])
+    check_glm_result(got, ref, "row-major x")
+
+
+def test_zero_instances_and_zero_attributes(glm, L):
+    # zero instances -> 0 (bernoulli_logit_glm_lpmf_test.cpp:110-145)
+    lp, _ = glm.poisson_log_glm_lpmf(np.zeros(0, np.int32), np.zeros((0, 3)), 0.3, [0.1, 0.2, 0.3])
+    assert lp == 0.0
+    # zero attributes -> eta = alpha (bernoulli_logit_glm_lpmf_test.cpp:147-175)
+    for fam, y, sg in (("bernoulli_logit", [1, 0, 1], None), ("poisson_log", [2, 0, 5], None),
+                       ("normal_id", [0.5, -1.0, 2.0], [1.7])):
+        ref = L.oracle_glm(fam, np.zeros((3, 0)), y, 0.3, np.zeros(0), sg)
+        got = glm.glm_eval(fam, y, np.zeros((3, 0)), 0.3, np.zeros(0), sg)
+        assert_close(got["lp"], ref["lp"], fam + " K=0 lp")
+        assert_close(got["dalpha"], ref["dalpha"], fam + " K=0 dalpha")
+
+
+def test_cutoff_branches_bit_exact_selection(glm, L):
+    """|ytheta| > 20 on both sides and near the cutoffs: same branch as the reference."""
+    eta = np.array([-40.0, -20.000001, -20.0, -19.999999, 0.0, 19.999999, 20.0, 20.000001, 40.0, 700.0, -700.0])
+    x = eta.reshape(-1, 1)
+    for y in ([1] * len(eta), [0] * len(eta)):
+        ref = L.oracle_glm("bernoulli_logit", x, y, np.zeros(len(eta)), [1.0])
+        got = glm.glm_eval("bernoulli_logit", y, x, np.zeros(len(eta)), [1.0])
+        assert_close(got["lp"], ref["lp"], "cutoff lp")
+        assert_close(got["dalpha"], ref["dalpha"], "cutoff d per row", 1e-13)
+
+
+def test_error_contract_lazy_checks(glm):
+    x = np.ones((3, 2))
+    with pytest.raises(glm.DomainError, match="Weight vector"):
+        glm.poisson_log_glm_lpmf([1, 0, 1], x, 0.3, [0.1, np.inf])
+    with pytest.raises(glm.DomainError, match="Intercept"):
+        glm.bernoulli_logit_glm_lpmf([1, 0, 1], x, np.nan, [0.1, 0.2])
+    xi = x.copy()
+    xi[0, 1] = np.nan
+    with pytest.raises(glm.DomainError, match="Matrix of independent variables"):
+        glm.bernoulli_logit_glm_lpmf([1, 0, 1], xi, 0.3, [0.1, 0.2])
+    with pytest.raises(glm.DomainError, match="Matrix of independent variables"):
+        glm.normal_id_glm_lpdf([1.0, 0.0, 1.0], xi, 0.3, [0.1, 0.2], [1.0])
+    # the reference's one-element check: NaN in a later row returns NaN without throwing
+    xi = x.copy()
+    xi[2, 0] = np.nan
+    lp, _ = glm.bernoulli_logit_glm_lpmf([1, 0, 1], xi, 0.3, [0.1, 0.2])
+    assert np.isnan(lp)
+
+
+def test_device_cache_hit_refill_and_invalidate(glm):
+    s = synth_glm("poisson_log", 20000, 24, seed=1)
+    glm.cache_clear()
+    st0 = glm.stats()
+    a = glm.glm_eval("poisson_log", s["y"], s["x"], s["alpha"], s["beta"])
+    b = glm.glm_eval("poisson_log", a["_keep"][1], a["_keep"][0], s["alpha"], s["beta"])
+    st1 = glm.stats()
+    assert st1["cache_misses"] - st0["cache_misses"] == 1 and st1["cache_hits"] - st0["cache_hits"] == 1
+    assert a["lp"] == b["lp"] and np.array_equal(a["dbeta"], b["dbeta"])  # deterministic, bit for bit
+    # same address, new content -> fingerprint mismatch -> refill, new value
+    x, y = a["_keep"]
+    x[:] = x * 0.5
+    c = glm.glm_eval("poisson_log", y, x, s["alpha"], s["beta"])
+    st2 = glm.stats()
+    assert st2["cache_misses"] - st1["cache_misses"] == 1 and c["lp"] != a["lp"]
+    assert glm.cache_invalidate(x) == 1
+    glm.cache_clear()
+
+
+def test_repeat_evaluations_are_bit_identical(glm):
+    s = synth_glm("bernoulli_logit", 250000, 32, seed=21)
+    r = [glm.glm_eval("bernoulli_logit", s["y"], s["x"], s["alpha"], s["beta"]) for _ in range(3)]
+    assert r[0]["lp"] == r[1]["lp"] == r[2]["lp"]
+    assert np.array_equal(r[0]["dbeta"], r[1]["dbeta"]) and np.array_equal(r[0]["dbeta"], r[2]["dbeta"])
+
+
+def test_large_shape_row_additivity(glm, L):
+    """Size-independent property at a large shape: value and gradient are sums over rows, so the
+    full evaluation equals the sum of the evaluations of two row blocks; a 4096-row sample is
+    also checked against the oracle."""
+    n, k = 1_000_000, 128
+    s = synth_glm("poisson_log", n, k, seed=1003)
+    full = glm.glm_eval("poisson_log", s["y"], s["x"], s["alpha"], s["beta"])
+    h = n // 2 + 12345
+    xa, xb = np.asfortranarray(s["x"][:h]), np.asfortranarray(s["x"][h:])
+    a = glm.glm_eval("poisson_log", s["y"][:h], xa, s["alpha"], s["beta"])
+    b = glm.glm_eval("poisson_log", s["y"][h:], xb, s["alpha"], s["beta"])
+    assert_close(a["lp"] + b["lp"], full["lp"], "additivity lp", 1e-12)
+    assert_close(a["dbeta"] + b["dbeta"], full["dbeta"], "additivity dbeta", 1e-11)
+    assert_close(a["dalpha"] + b["dalpha"], full["dalpha"], "additivity dalpha", 1e-11)
+    xs = np.asfortranarray(s["x"][:4096])
+    ref = L.oracle_glm("poisson_log", xs, s["y"][:4096], s["alpha"], s["beta"])
+    got = glm.glm_eval("poisson_log", s["y"][:4096], xs, s["alpha"], s["beta"])
+    check_glm_result(got, ref, "sample of the large shape")
+    glm.cache_clear()
+
+
+def test_device_level_launch_matches_host_level(glm):
+    import torch
+    s = synth_glm("normal_id", 60000, 64, seed=8)
+    host = glm.glm_eval("normal_id", s["y"], s["x"], s["alpha"], s["beta"], s["sigma"])
+    d = glm.GlmData("normal_id", s["x"], s["y"])
+    params = np.zeros(d.params_len)
+    params[:64], params[d.kpad], params[d.kpad + 1] = s["beta"], s["alpha"][0], s["sigma"][0]
+    dp = torch.from_numpy(params).cuda()
+    dr = torch.zeros(d.result_len, dtype=torch.float64, device="cuda")
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        d.launch(glm.glm_flags(_abi.NORMAL_ID, False), dp.data_ptr(), dr.data_ptr(), stream.cuda_stream)
+    stream.synchronize()
+    res = dr.cpu().numpy()
+    assert res[0] == host["lp"] and np.array_equal(res[4:4 + 64], host["dbeta"])
+    assert res[1] == host["dalpha"][0] and res[2] == host["dsigma"][0]
+    d.close()
+
+
+def test_normal_lpdf_against_oracle_large(glm, L):
+    rng = np.random.default_rng(5)
+    n = 1_000_000
+    y, mu = rng.standard_normal(n), 0.1 * rng.standard_normal(n)
+    ref = L.oracle_normal_lpdf(y, mu, [1.3])
+    lp, g = glm.normal_lpdf(y, mu, [1.3])
+    assert_close(lp, ref["lp"], "normal_lpdf lp")
+    assert_close(g["mu"], ref["dmu"], "normal_lpdf dmu")
+    assert_close(g["sigma"], ref["dsigma"], "normal_lpdf dsigma")
+    glm.cache_clear()
+
+
+def test_concurrent_host_threads(glm, L):
+    """TBB-style concurrency: several host threads evaluate different GLMs at once."""
+    import threading
+    cases = [synth_glm("poisson_log", 20000 + 1000 * i, 16 + i, seed=50 + i) for i in range(6)]
+    refs = [L.oracle_glm("poisson_log", c["x"], c["y"], c["alpha"], c["beta"]) for c in cases]
+    out, errs = [None] * len(cases), []
+
+    def work(i):
+        try:
+            for _ in range(5):
+                out[i] = glm.glm_eval("poisson_log", cases[i]["y"], cases[i]["x"], cases[i]["alpha"], cases[i]["beta"])
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(len(cases))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    for got, ref in zip(out, refs):
+        check_glm_result(got, ref, "threaded")
+    glm.cache_clear()
+
+
+def test_shard_scope_keys_by_call_id_and_job(glm, L):
+    """Inside a map_rect shard scope the data identity is (call_id, job): a functor that rebuilds
+    X at a new address on every call still hits the cache."""
+    s = synth_glm("bernoulli_logit", 10000, 32, seed=77)
+    ref = L.oracle_glm("bernoulli_logit", s["x"], s["y"], s["alpha"], s["beta"])
+    st0 = glm.stats()
+    for rep in range(3):
+        x_tmp = np.array(s["x"], order="F", copy=True)  # fresh temporary, like the functor's Eigen matrix
+        with glm.shard_scope(call_id=5, job=2, device=0):
+            got = glm.glm_eval("bernoulli_logit", s["y"].copy(), x_tmp, s["alpha"], s["beta"])
+        check_glm_result(got, ref, "shard scope rep %d" % rep)
+    st1 = glm.stats()
+    assert st1["cache_misses"] - st0["cache_misses"] == 1 and st1["cache_hits"] - st0["cache_hits"] == 2
+    glm.cache_clear()

@@ -1,0 +1,113 @@
+"""CPU tests (no GPU): the plain-C oracle against the reference's golden vectors, and against
+the compiled reference itself when oracle/_ref/libstanref.so is present."""
+import numpy as np
+import pytest
+
+from oracle import loader as L
+from tests.helpers import assert_close, check_glm_result, glm_case, normal_case, synth_glm
+from math_b200 import _abi
+
+
+def test_golden_file_has_cases(golden):
+    assert len(golden["glm_cases"]) >= 30 and len(golden["normal_cases"]) >= 8
+
+
+def test_oracle_glm_matches_golden(golden):
+    for name in golden["glm_cases"]:
+        c = glm_case(golden, str(name))
+        r = L.oracle_glm(c["family"], c["x"], c["y"], c["alpha"], c["beta"], c["sigma"],
+                         propto=c["propto"], need_dy=c["need_dy"])
+        assert r["rc"] == 0, name
+        check_glm_result(r, c, "oracle vs golden " + str(name), rtol=1e-11)
+
+
+def test_oracle_normal_matches_golden_and_known_answers(golden):
+    for name in golden["normal_cases"]:
+        c = normal_case(golden, str(name))
+        r = L.oracle_normal_lpdf(c["y"], c["mu"], c["sigma"], propto=c["propto"], need_dy=c["need_dy"])
+        assert_close(r["lp"], c["lp"], str(name) + " lp", 1e-12)
+        assert_close(r["dmu"], c["dmu"], str(name) + " dmu", 1e-12)
+        assert_close(r["dsigma"], c["dsigma"], str(name) + " dsigma", 1e-11)
+        if c["need_dy"]:
+            assert_close(r["dy"], c["dy"], str(name) + " dy", 1e-12)
+        if "known_answer" in c:  # literals of test/prob/normal/normal_test.hpp:11-40
+            assert abs(r["lp"] - c["known_answer"]) < 1e-14 * max(1, abs(c["known_answer"]))
+            assert abs(c["lp"] - c["known_answer"]) < 1e-14 * max(1, abs(c["known_answer"]))
+
+
+def test_oracle_reference_quirks():
+    """Behaviours of the reference a 'cleaner' implementation would miss."""
+    x = np.array([[-12, 46], [-42, 24], [25, 27]], float) * 0.01
+    # poisson<propto=true> with var arguments returns 0 but keeps its gradient
+    r = L.oracle_glm("poisson_log", x, [15, 3, 5], 0.3, [0.3, 2.0], propto=True)
+    assert r["lp"] == 0.0 and np.all(r["dbeta"] != 0)
+    # bernoulli: for ytheta > 20 the derivative is -exp(-ytheta), without the sign factor
+    xe = np.array([[30.0]])
+    r = L.oracle_glm("bernoulli_logit", xe, [1], 0.0, [1.0])
+    assert r["dalpha"][0] == -np.exp(-30.0)
+    r = L.oracle_glm("bernoulli_logit", xe, [0], 0.0, [1.0])   # ytheta = -30 < -20: d = sign = -1
+    assert r["dalpha"][0] == -1.0 and r["lp"] == -30.0
+
+
+def test_oracle_nonfinite_status():
+    x = np.array([[1.0, 2.0], [3.0, np.inf]])
+    assert L.oracle_glm("poisson_log", x, [1, 2], 0.1, [0.5, 0.5])["rc"] == _abi.NONFINITE
+    assert L.oracle_glm("normal_id", x, [1.0, 2.0], 0.1, [0.5, 0.5], [1.0])["rc"] == _abi.NONFINITE
+    assert L.oracle_glm("bernoulli_logit", x * np.nan, [1, 0], 0.1, [0.5, 0.5])["rc"] == _abi.NONFINITE
+
+
+needs_ref = pytest.mark.skipif(not L.have_ref(), reason="oracle/_ref/libstanref.so not built")
+
+
+@needs_ref
+@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id"])
+@pytest.mark.parametrize("n,k", [(1, 1), (7, 3), (500, 32), (1200, 130)])
+def test_oracle_vs_compiled_reference(family, n, k):
+    s = synth_glm(family, n, k, seed=n * 131 + k)
+    for propto in (False, True):
+        ref = L.ref_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"], propto=propto)
+        got = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"], propto=propto)
+        check_glm_result(got, ref, "%s %dx%d propto=%s" % (family, n, k, propto), rtol=1e-11)
+
+
+@needs_ref
+def test_reference_error_contract():
+    """What the reference throws (the boundary must reproduce it): sizes -> invalid_argument (2),
+    domain violations -> domain_error (1)."""
+    x = np.ones((3, 2))
+    with pytest.raises(L.RefError) as e:
+        L.ref_glm("bernoulli_logit", x, [1, 0, 23], 0.3, [0.1, 0.2])
+    assert e.value.rc == 1
+    with pytest.raises(L.RefError) as e:
+        L.ref_glm("poisson_log", x, [1, 0, -1], 0.3, [0.1, 0.2])
+    assert e.value.rc == 1
+    with pytest.raises(L.RefError) as e:
+        L.ref_glm("normal_id", x, [1.0, 0.0, 2.0], 0.3, [0.1, 0.2], [-1.0])
+    assert e.value.rc == 1
+    with pytest.raises(L.RefError) as e:
+        L.ref_glm("poisson_log", x, [1, 0, 1], 0.3, [0.1, np.inf])
+    assert e.value.rc == 1 and "Weight vector" in str(e.value)
+    xi = x.copy()
+    xi[0, 1] = np.nan  # row 0: the reference's lazy check only looks at the first row (see below)
+    with pytest.raises(L.RefError) as e:
+        L.ref_glm("bernoulli_logit", xi, [1, 0, 1], 0.3, [0.1, 0.2])
+    assert e.value.rc == 1 and "Matrix of independent variables" in str(e.value)
+    # quirk: check_finite on the Eigen::Array ytheta inspects ONE element, so a NaN in another row
+    # comes back as a NaN log-density without any exception
+    xi = x.copy()
+    xi[1, 1] = np.nan
+    r = L.ref_glm("bernoulli_logit", xi, [1, 0, 1], 0.3, [0.1, 0.2])
+    assert np.isnan(r["lp"])
+
+
+@needs_ref
+def test_reference_map_rect_baseline_matches_plain_call():
+    """The TBB map_rect row-sharded baseline computes the same value and gradient as one call."""
+    s = synth_glm("poisson_log", 4000, 16, seed=5)
+    plain = L.ref_glm("poisson_log", s["x"], s["y"], s["alpha"], s["beta"])
+    sh = L.RefShards("poisson_log", s["x"], s["y"], n_shards=8, n_threads=4)
+    r = sh.eval(s["beta"], alpha=s["alpha"])
+    sh.close()
+    assert_close(r["lp"], plain["lp"], "map_rect lp", 1e-12)
+    assert_close(r["dbeta"], plain["dbeta"], "map_rect dbeta", 1e-11)
+    assert_close(r["dalpha"], plain["dalpha"], "map_rect dalpha", 1e-11)
