@@ -142,6 +142,11 @@ STAN_CUDA_API void stan_cuda_stats_reset(void);
 /* Rows are sharded over all devices of the process only when n*k reaches this many elements
  * (default 1<<24); smaller problems stay on one device. */
 STAN_CUDA_API void stan_cuda_set_shard_min_elems(int64_t elems);
+/* Kernel tuning knobs (cf. opencl_context_base::tuning_opts_, stan/math/opencl/opencl_context.hpp:164-183):
+ * consumer threads per CTA (128|256|512; fixes the tile shape of data created afterwards), TMA
+ * pipeline stages and resident CTAs per SM.  0 = automatic, negative = leave unchanged.
+ * Environment: STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM. */
+STAN_CUDA_API void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm);
 
 /* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */
 STAN_CUDA_API int stan_cuda_glm_eval(const stan_cuda_glm_args* a);

@@ -376,7 +376,7 @@ static int env_int(const char* name, int dflt) {
   return atoi(v);
 }
 
-const Tuning& tuning() {
+static Tuning& tuning_mut() {
   static Tuning t = [] {
     Tuning u;
     u.threads = env_int("STAN_CUDA_THREADS", 0);
@@ -386,6 +386,8 @@ const Tuning& tuning() {
   }();
   return t;
 }
+
+const Tuning& tuning() { return tuning_mut(); }
 
 int sm_count(int device) {
   static int cached[64] = {0};
@@ -517,3 +519,10 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
 }
 
 }  // namespace stancuda
+
+extern "C" void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm) {
+  stancuda::Tuning& t = stancuda::tuning_mut();
+  if (threads >= 0) t.threads = threads;
+  if (stages >= 0) t.stages = stages;
+  if (ctas_per_sm >= 0) t.ctas_per_sm = ctas_per_sm;
+}
