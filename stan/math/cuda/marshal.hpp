@@ -1,0 +1,206 @@
+#ifndef STAN_MATH_CUDA_MARSHAL_HPP
+#define STAN_MATH_CUDA_MARSHAL_HPP
+#ifdef STAN_CUDA
+
+// Compile-time routing and marshalling between the reference's argument kinds and the C ABI.
+// C++14 only (the reference builds with -std=c++1y): overloads and tag types, no if constexpr.
+
+#include <stan/math/prim/mat/fun/Eigen.hpp>
+#include <stan/math/prim/meta.hpp>
+#include <stan/math/prim/scal/fun/value_of_rec.hpp>
+#include <stan/math/rev/core.hpp>
+#include <stan/math/rev/meta.hpp>
+#include <type_traits>
+#include <vector>
+
+namespace stan {
+namespace math {
+namespace cuda {
+
+// ---- which instantiations take the GPU path ---------------------------------------
+template <typename T>
+struct is_double_or_var
+    : std::integral_constant<bool, std::is_same<T, double>::value || std::is_same<T, var>::value> {};
+
+/** x: an Eigen matrix of doubles (data).  var / fvar matrices stay on the reference body. */
+template <typename T>
+struct is_data_matrix : std::false_type {};
+template <int R, int C, int O, int MR, int MC>
+struct is_data_matrix<Eigen::Matrix<double, R, C, O, MR, MC>> : std::true_type {};
+
+/** scalar, std::vector or Eigen vector whose scalar type satisfies Pred */
+template <typename T, template <typename> class Pred>
+struct is_scalar_or_vector_of : Pred<T> {};
+template <typename T, template <typename> class Pred>
+struct is_scalar_or_vector_of<std::vector<T>, Pred> : Pred<T> {};
+template <typename T, int R, int C, int O, int MR, int MC, template <typename> class Pred>
+struct is_scalar_or_vector_of<Eigen::Matrix<T, R, C, O, MR, MC>, Pred>
+    : std::integral_constant<bool, Pred<T>::value && (R == 1 || C == 1)> {};
+
+template <typename T>
+struct is_int_scalar : std::is_same<T, int> {};
+template <typename T>
+struct is_double_int_or_var
+    : std::integral_constant<bool, is_double_or_var<T>::value || std::is_same<T, int>::value> {};
+
+/** parameters (alpha, beta, sigma, mu): double / int / var, scalar or vector */
+template <typename T>
+struct is_param_arg : is_scalar_or_vector_of<T, is_double_int_or_var> {};
+/** integer outcomes (bernoulli, poisson): int scalar / std::vector<int> / Eigen int vector */
+template <typename T>
+struct is_int_outcome : is_scalar_or_vector_of<T, is_int_scalar> {};
+/** real outcomes (normal): double or var, scalar or vector */
+template <typename T>
+struct is_real_outcome : is_scalar_or_vector_of<T, is_double_or_var> {};
+
+template <typename T_y, typename T_x, typename T_alpha, typename T_beta>
+struct int_glm_eligible
+    : std::integral_constant<bool, is_int_outcome<T_y>::value && is_data_matrix<T_x>::value
+                                       && is_param_arg<T_alpha>::value && is_param_arg<T_beta>::value> {};
+
+template <typename T_y, typename T_x, typename T_alpha, typename T_beta, typename T_scale>
+struct normal_glm_eligible
+    : std::integral_constant<bool, is_real_outcome<T_y>::value && is_data_matrix<T_x>::value
+                                       && is_param_arg<T_alpha>::value && is_param_arg<T_beta>::value
+                                       && is_param_arg<T_scale>::value> {};
+
+// ---- values of an argument as contiguous doubles ------------------------------------------------
+/**
+ * View of the values of a scalar / std::vector / Eigen vector argument as `size()` contiguous
+ * doubles.  Double containers are borrowed (no copy, stable address -> usable as a cache
+ * identity); everything else is copied with value_of_rec.
+ */
+template <typename T>
+class values {
+ public:
+  explicit values(const T& v) : owned_(length(v)) {
+    scalar_seq_view<T> view(v);
+    for (size_t i = 0; i < owned_.size(); ++i) {
+      owned_[i] = value_of_rec(view[i]);
+    }
+    ptr_ = owned_.data();
+    size_ = owned_.size();
+  }
+  const double* data() const { return ptr_; }
+  size_t size() const { return size_; }
+  bool borrowed() const { return false; }
+
+ private:
+  std::vector<double> owned_;
+  const double* ptr_;
+  size_t size_;
+};
+
+template <>
+class values<std::vector<double>> {
+ public:
+  explicit values(const std::vector<double>& v) : ptr_(v.data()), size_(v.size()) {}
+  const double* data() const { return ptr_; }
+  size_t size() const { return size_; }
+  bool borrowed() const { return true; }
+
+ private:
+  const double* ptr_;
+  size_t size_;
+};
+
+template <int R, int C, int O, int MR, int MC>
+class values<Eigen::Matrix<double, R, C, O, MR, MC>> {
+ public:
+  explicit values(const Eigen::Matrix<double, R, C, O, MR, MC>& v) : ptr_(v.data()), size_(v.size()) {}
+  const double* data() const { return ptr_; }
+  size_t size() const { return size_; }
+  bool borrowed() const { return true; }
+
+ private:
+  const double* ptr_;
+  size_t size_;
+};
+
+/** Outcome vector of exactly n doubles: a scalar outcome is broadcast (the reference's
+ * as_array_or_scalar does the same implicitly). */
+template <typename T>
+class real_outcome {
+ public:
+  real_outcome(const T& y, size_t n) : vals_(y) {
+    if (vals_.size() == n) {
+      ptr_ = vals_.data();
+    } else {
+      expanded_.assign(n, vals_.size() ? vals_.data()[0] : 0.0);
+      ptr_ = expanded_.data();
+    }
+  }
+  const double* data() const { return ptr_; }
+
+ private:
+  values<T> vals_;
+  std::vector<double> expanded_;
+  const double* ptr_;
+};
+
+/** Integer outcome vector of exactly n int32: borrowed when the caller holds ints already. */
+template <typename T>
+class int_outcome;
+
+template <>
+class int_outcome<int> {
+ public:
+  int_outcome(const int& y, size_t n) : owned_(n, y) {}
+  const int* data() const { return owned_.data(); }
+
+ private:
+  std::vector<int> owned_;
+};
+
+template <>
+class int_outcome<std::vector<int>> {
+ public:
+  int_outcome(const std::vector<int>& y, size_t /*n*/) : ptr_(y.data()) {}
+  const int* data() const { return ptr_; }
+
+ private:
+  const int* ptr_;
+};
+
+template <int R, int C, int O, int MR, int MC>
+class int_outcome<Eigen::Matrix<int, R, C, O, MR, MC>> {
+ public:
+  int_outcome(const Eigen::Matrix<int, R, C, O, MR, MC>& y, size_t /*n*/) : ptr_(y.data()) {}
+  const int* data() const { return ptr_; }
+
+ private:
+  const int* ptr_;
+};
+
+// ---- where the partials of an operands_and_partials edge live --------------------------------
+// Constant operands have an empty edge (prim/scal/meta/operands_and_partials.hpp:35-51): nullptr.
+template <typename ViewElt, typename Op>
+inline double* partials_data(internal::ops_partials_edge<ViewElt, Op>& /*edge*/) {
+  return nullptr;
+}
+inline double* partials_data(internal::ops_partials_edge<double, var>& edge) { return &edge.partial_; }
+inline double* partials_data(internal::ops_partials_edge<double, std::vector<var>>& edge) {
+  return edge.partials_.data();
+}
+template <int R, int C>
+inline double* partials_data(internal::ops_partials_edge<double, Eigen::Matrix<var, R, C>>& edge) {
+  return edge.partials_.data();
+}
+
+/** Matrix layout as the C ABI wants it. */
+template <int R, int C, int O, int MR, int MC>
+inline void matrix_layout(const Eigen::Matrix<double, R, C, O, MR, MC>& x, const double** data, int64_t* ld,
+                          int32_t* row_major) {
+  *data = x.data();
+  *row_major = (O & Eigen::RowMajor) ? 1 : 0;
+  *ld = *row_major ? x.cols() : x.rows();
+  if (*ld < 1) {
+    *ld = 1;
+  }
+}
+
+}  // namespace cuda
+}  // namespace math
+}  // namespace stan
+#endif
+#endif

@@ -1,0 +1,101 @@
+#ifndef STAN_MATH_CUDA_NORMAL_ID_GLM_LPDF_HPP
+#define STAN_MATH_CUDA_NORMAL_ID_GLM_LPDF_HPP
+#ifdef STAN_CUDA
+
+#include <stan/math/cuda/glm_call.hpp>
+#include <stan/math/prim/scal/err/check_consistent_size.hpp>
+#include <stan/math/prim/scal/err/check_consistent_sizes.hpp>
+#include <stan/math/prim/scal/err/check_finite.hpp>
+#include <stan/math/prim/scal/err/check_positive_finite.hpp>
+#include <stan/math/prim/scal/fun/size_zero.hpp>
+
+namespace stan {
+namespace math {
+namespace cuda {
+
+/**
+ * GPU body of normal_id_glm_lpdf (reference: stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp).
+ * Checks :70-88 unchanged (check_positive_finite(sigma) is eager and first); partials for y,
+ * alpha, beta, sigma go straight into edges 1, 3, 4, 5; lazy checks as :150-156.
+ */
+template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta, typename T_scale>
+return_type_t<T_y, T_x, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y& y, const T_x& x,
+                                                                            const T_alpha& alpha,
+                                                                            const T_beta& beta,
+                                                                            const T_scale& sigma) {
+  static const char* function = "normal_id_glm_lpdf";
+  const size_t N = x.rows();
+  const size_t M = x.cols();
+
+  check_positive_finite(function, "Scale vector", sigma);
+  check_consistent_size(function, "Vector of dependent variables", y, N);
+  check_consistent_size(function, "Weight vector", beta, M);
+  if (is_vector<T_scale>::value) {
+    check_consistent_sizes(function, "Vector of scale parameters", sigma, "Vector of dependent variables", y);
+  }
+  if (is_vector<T_alpha>::value) {
+    check_consistent_sizes(function, "Vector of intercepts", alpha, "Vector of dependent variables", y);
+  }
+  if (size_zero(y, sigma)) {
+    return 0;
+  }
+  if (!include_summand<propto, T_y, T_x, T_alpha, T_beta, T_scale>::value) {
+    return 0;
+  }
+
+  real_outcome<T_y> y_val(y, N);
+  values<T_scale> sigma_val(sigma);
+  glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_NORMAL_ID, x, alpha, beta);
+  operands_and_partials<T_y, T_x, T_alpha, T_beta, T_scale> ops_partials(y, x, alpha, beta, sigma);
+  stan_cuda_glm_args& a = call.args();
+  a.y = y_val.data();
+  a.y_is_double = 1;
+  a.sigma = sigma_val.data();
+  a.sigma_len = sigma_val.size();
+  a.flags = 0;
+  if (include_summand<propto>::value) {
+    a.flags |= STAN_CUDA_LP_CONST;
+  }
+  if (include_summand<propto, T_scale>::value) {
+    a.flags |= STAN_CUDA_LP_SCALE;
+  }
+  a.flags |= STAN_CUDA_LP_MAIN;  // include_summand<propto, all five> holds past the early return
+  if (!is_constant_all<T_y>::value) {
+    if (is_vector<T_y>::value) {  // per-row partials; a scalar var y gets the sum below
+      a.flags |= STAN_CUDA_NEED_DY;
+      a.dy = partials_data(ops_partials.edge1_);
+    }
+  }
+  if (!is_constant_all<T_alpha>::value) {
+    a.flags |= STAN_CUDA_NEED_DALPHA;
+    a.dalpha = partials_data(ops_partials.edge3_);
+  }
+  if (!is_constant_all<T_beta>::value) {
+    a.flags |= STAN_CUDA_NEED_DBETA;
+    a.dbeta = partials_data(ops_partials.edge4_);
+  }
+  if (!is_constant_all<T_scale>::value) {
+    a.flags |= STAN_CUDA_NEED_DSIGMA;
+    a.dsigma = partials_data(ops_partials.edge5_);
+  }
+  if (!call.run(function)) {
+    const double y_scaled_sq_sum = call.witness();
+    check_finite(function, "Vector of dependent variables", y);
+    check_finite(function, "Weight vector", beta);
+    check_finite(function, "Intercept", alpha);
+    check_finite(function, "Matrix of independent variables", y_scaled_sq_sum);
+  }
+  if (!is_constant_all<T_y>::value && !is_vector<T_y>::value) {
+    double* dy = partials_data(ops_partials.edge1_);
+    if (dy) {
+      *dy = -call.sum_d();  // sum of -mu_derivative over the rows the scalar is broadcast to
+    }
+  }
+  return ops_partials.build(call.logp());
+}
+
+}  // namespace cuda
+}  // namespace math
+}  // namespace stan
+#endif
+#endif

@@ -1,0 +1,304 @@
+// GPU-vs-CPU parity of the STAN_CUDA path through the reference's own C++ signatures.
+// Modelled on the reference's OpenCL-vs-CPU tests (test/unit/math/opencl/rev/*_glm_*_test.cpp):
+// same sizes (3x2 fixtures, N = 0, M = 0, vector alpha / sigma, "big" 153 x 71) and the same
+// error cases, but at the north star's tolerance of 1e-10 instead of 1e-8.  The CPU side is the
+// unmodified reference body, reachable in the same binary as *_reference_cpu (see overlay/).
+#ifdef STAN_CUDA
+#include <stan/math.hpp>
+#include <gtest/gtest.h>
+#include <random>
+#include <vector>
+
+using Eigen::Dynamic;
+using Eigen::Matrix;
+using Eigen::MatrixXd;
+using Eigen::VectorXd;
+using stan::math::var;
+typedef Matrix<var, Dynamic, 1> vector_v;
+
+namespace {
+
+void expect_rel(double got, double ref, double scale, const char* what) {
+  const double denom = std::max(std::fabs(ref), 1e-6 * scale);
+  if (denom == 0) {
+    EXPECT_EQ(got, ref) << what;
+  } else {
+    EXPECT_LE(std::fabs(got - ref) / denom, 1e-10) << what << " got " << got << " ref " << ref;
+  }
+}
+
+void expect_vec(const VectorXd& got, const VectorXd& ref, const char* what) {
+  ASSERT_EQ(got.size(), ref.size()) << what;
+  const double scale = ref.size() ? ref.cwiseAbs().maxCoeff() : 0.0;
+  for (int i = 0; i < ref.size(); ++i) {
+    expect_rel(got[i], ref[i], scale, what);
+  }
+}
+
+VectorXd adj(const vector_v& v) {
+  VectorXd a(v.size());
+  for (int i = 0; i < v.size(); ++i) a[i] = v[i].adj();
+  return a;
+}
+
+vector_v to_v(const VectorXd& d) {
+  vector_v v(d.size());
+  for (int i = 0; i < d.size(); ++i) v[i] = d[i];
+  return v;
+}
+
+struct Problem {
+  MatrixXd x;
+  std::vector<int> y_bern, y_pois;
+  VectorXd y_norm, beta, alpha_vec, sigma_vec;
+  double alpha, sigma;
+};
+
+Problem make_problem(int n, int k, unsigned seed) {
+  std::mt19937_64 rng(seed);
+  std::normal_distribution<double> nd(0, 1);
+  std::uniform_real_distribution<double> ud(0, 1);
+  Problem p;
+  p.x.resize(n, k);
+  for (int j = 0; j < k; ++j)
+    for (int i = 0; i < n; ++i) p.x(i, j) = nd(rng);
+  VectorXd beta_true(k);
+  for (int j = 0; j < k; ++j) beta_true[j] = nd(rng) * 0.6 / std::sqrt(std::max(k, 1));
+  p.beta = beta_true;
+  for (int j = 0; j < k; ++j) p.beta[j] += 0.05 * nd(rng);
+  p.alpha = 0.3;
+  p.sigma = 1.3;
+  p.y_bern.resize(n);
+  p.y_pois.resize(n);
+  p.y_norm.resize(n);
+  p.alpha_vec.resize(n);
+  p.sigma_vec.resize(n);
+  for (int i = 0; i < n; ++i) {
+    double eta = 0.2 + (k ? p.x.row(i).dot(beta_true) : 0.0);
+    p.y_bern[i] = ud(rng) < 1 / (1 + std::exp(-eta)) ? 1 : 0;
+    p.y_pois[i] = std::poisson_distribution<int>(std::exp(eta))(rng);
+    p.y_norm[i] = eta + 0.7 * nd(rng);
+    p.alpha_vec[i] = 0.3 + 0.1 * nd(rng);
+    p.sigma_vec[i] = 0.5 + ud(rng);
+  }
+  return p;
+}
+
+}  // namespace
+
+#define STAN_CUDA_PARITY(NAME, GPU_CALL, CPU_CALL, ...)                                     \
+  {                                                                                         \
+    var lp_gpu = GPU_CALL;                                                                  \
+    lp_gpu.grad();                                                                          \
+    const double v_gpu = lp_gpu.val();                                                      \
+    std::vector<VectorXd> g_gpu = {__VA_ARGS__};                                            \
+    stan::math::set_zero_all_adjoints();                                                    \
+    var lp_cpu = CPU_CALL;                                                                  \
+    lp_cpu.grad();                                                                          \
+    std::vector<VectorXd> g_cpu = {__VA_ARGS__};                                            \
+    expect_rel(v_gpu, lp_cpu.val(), std::fabs(lp_cpu.val()), NAME " value");                \
+    for (size_t q = 0; q < g_cpu.size(); ++q) expect_vec(g_gpu[q], g_cpu[q], NAME " grad"); \
+    stan::math::set_zero_all_adjoints();                                                    \
+  }
+
+class CudaGlm : public ::testing::TestWithParam<std::pair<int, int>> {};
+
+TEST_P(CudaGlm, bernoulli_poisson_normal_match_reference_body) {
+  const int n = GetParam().first, k = GetParam().second;
+  Problem p = make_problem(n, k, 1000 + n + k);
+  vector_v beta = to_v(p.beta);
+  var alpha = p.alpha, sigma = p.sigma;
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("bernoulli", bernoulli_logit_glm_lpmf(p.y_bern, p.x, alpha, beta),
+                   bernoulli_logit_glm_lpmf_reference_cpu(p.y_bern, p.x, alpha, beta), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()));
+  STAN_CUDA_PARITY("bernoulli propto", bernoulli_logit_glm_lpmf<true>(p.y_bern, p.x, alpha, beta),
+                   bernoulli_logit_glm_lpmf_reference_cpu<true>(p.y_bern, p.x, alpha, beta), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()));
+  STAN_CUDA_PARITY("poisson", poisson_log_glm_lpmf(p.y_pois, p.x, alpha, beta),
+                   poisson_log_glm_lpmf_reference_cpu(p.y_pois, p.x, alpha, beta), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()));
+  STAN_CUDA_PARITY("poisson propto", poisson_log_glm_lpmf<true>(p.y_pois, p.x, alpha, beta),
+                   poisson_log_glm_lpmf_reference_cpu<true>(p.y_pois, p.x, alpha, beta), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()));
+  STAN_CUDA_PARITY("normal_id", normal_id_glm_lpdf(p.y_norm, p.x, alpha, beta, sigma),
+                   normal_id_glm_lpdf_reference_cpu(p.y_norm, p.x, alpha, beta, sigma), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, sigma.adj()));
+  STAN_CUDA_PARITY("normal_id propto", normal_id_glm_lpdf<true>(p.y_norm, p.x, alpha, beta, sigma),
+                   normal_id_glm_lpdf_reference_cpu<true>(p.y_norm, p.x, alpha, beta, sigma), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, sigma.adj()));
+  // all-double call returns a double through the same device path
+  EXPECT_NEAR(poisson_log_glm_lpmf(p.y_pois, p.x, p.alpha, p.beta),
+              poisson_log_glm_lpmf_reference_cpu(p.y_pois, p.x, p.alpha, p.beta),
+              1e-10 * std::fabs(poisson_log_glm_lpmf_reference_cpu(p.y_pois, p.x, p.alpha, p.beta)) + 1e-300);
+  stan::math::recover_memory();
+}
+
+INSTANTIATE_TEST_CASE_P(Shapes, CudaGlm,
+                        ::testing::Values(std::make_pair(3, 2), std::make_pair(1, 1), std::make_pair(153, 71),
+                                          std::make_pair(5000, 32), std::make_pair(20000, 128),
+                                          std::make_pair(3000, 256), std::make_pair(40, 0)));
+
+TEST(CudaGlmVariants, vector_alpha_vector_sigma_var_y) {
+  Problem p = make_problem(153, 71, 7);
+  vector_v beta = to_v(p.beta), alpha_v = to_v(p.alpha_vec), sigma_v = to_v(p.sigma_vec), y_v = to_v(p.y_norm);
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("bernoulli vector alpha", bernoulli_logit_glm_lpmf(p.y_bern, p.x, alpha_v, beta),
+                   bernoulli_logit_glm_lpmf_reference_cpu(p.y_bern, p.x, alpha_v, beta), adj(beta), adj(alpha_v));
+  STAN_CUDA_PARITY("poisson vector alpha", poisson_log_glm_lpmf(p.y_pois, p.x, alpha_v, beta),
+                   poisson_log_glm_lpmf_reference_cpu(p.y_pois, p.x, alpha_v, beta), adj(beta), adj(alpha_v));
+  STAN_CUDA_PARITY("normal all vectors + var y", normal_id_glm_lpdf(y_v, p.x, alpha_v, beta, sigma_v),
+                   normal_id_glm_lpdf_reference_cpu(y_v, p.x, alpha_v, beta, sigma_v), adj(beta), adj(alpha_v),
+                   adj(sigma_v), adj(y_v));
+  // std::vector<var> and row-vector operands
+  std::vector<var> beta_std(p.beta.data(), p.beta.data() + p.beta.size());
+  Matrix<var, 1, Dynamic> beta_row = beta.transpose();
+  var alpha = 0.3;
+  var a = poisson_log_glm_lpmf(p.y_pois, p.x, alpha, beta_std);
+  var b = poisson_log_glm_lpmf(p.y_pois, p.x, alpha, beta_row);
+  var c = poisson_log_glm_lpmf_reference_cpu(p.y_pois, p.x, alpha, beta);
+  expect_rel(a.val(), c.val(), std::fabs(c.val()), "std::vector<var> beta");
+  expect_rel(b.val(), c.val(), std::fabs(c.val()), "row-vector beta");
+  // Eigen int outcome vector
+  Matrix<int, Dynamic, 1> y_eig = Eigen::Map<Matrix<int, Dynamic, 1>>(p.y_pois.data(), p.y_pois.size());
+  var d = poisson_log_glm_lpmf(y_eig, p.x, alpha, beta);
+  expect_rel(d.val(), c.val(), std::fabs(c.val()), "Eigen int y");
+  stan::math::recover_memory();
+}
+
+TEST(CudaGlmVariants, zero_instances) {
+  MatrixXd x(0, 2);
+  std::vector<int> y;
+  VectorXd yn(0);
+  vector_v beta(2);
+  beta << 0.3, 2;
+  var alpha = 0.3, sigma = 2.0;
+  EXPECT_EQ(0, stan::math::bernoulli_logit_glm_lpmf(y, x, alpha, beta).val());
+  EXPECT_EQ(0, stan::math::poisson_log_glm_lpmf(y, x, alpha, beta).val());
+  EXPECT_EQ(0, stan::math::normal_id_glm_lpdf(yn, x, alpha, beta, sigma).val());
+  stan::math::recover_memory();
+}
+
+TEST(CudaGlmErrors, same_exceptions_as_the_reference) {
+  using stan::math::bernoulli_logit_glm_lpmf;
+  using stan::math::normal_id_glm_lpdf;
+  using stan::math::poisson_log_glm_lpmf;
+  MatrixXd x(3, 2);
+  x << -12, 46, -42, 24, 25, 27;
+  x *= 0.01;
+  std::vector<int> y{1, 0, 1}, y_size{1, 0, 1, 0}, y_val{1, 0, 23}, y_neg{1, 0, -1};
+  VectorXd yn(3), beta(2), beta_size(3), beta_inf(2), sigma_v(3);
+  yn << 0.1, 0.2, 0.3;
+  beta << 0.3, 2;
+  beta_size << 0.3, 2, 1;
+  beta_inf << 0.3, INFINITY;
+  double alpha = 0.3;
+  EXPECT_THROW(bernoulli_logit_glm_lpmf(y_size, x, alpha, beta), std::invalid_argument);
+  EXPECT_THROW(bernoulli_logit_glm_lpmf(y, x, alpha, beta_size), std::invalid_argument);
+  EXPECT_THROW(bernoulli_logit_glm_lpmf(y_val, x, alpha, beta), std::domain_error);
+  EXPECT_THROW(poisson_log_glm_lpmf(y_neg, x, alpha, beta), std::domain_error);
+  EXPECT_THROW(poisson_log_glm_lpmf(y, x, alpha, beta_inf), std::domain_error);
+  EXPECT_THROW(poisson_log_glm_lpmf(y, x, NAN, beta), std::domain_error);
+  EXPECT_THROW(normal_id_glm_lpdf(yn, x, alpha, beta, 0.0), std::domain_error);
+  EXPECT_THROW(normal_id_glm_lpdf(yn, x, alpha, beta, INFINITY), std::domain_error);
+  MatrixXd x_bad = x;
+  x_bad(0, 1) = NAN;
+  EXPECT_THROW(bernoulli_logit_glm_lpmf(y, x_bad, alpha, beta), std::domain_error);
+  EXPECT_THROW(poisson_log_glm_lpmf(y, x_bad, alpha, beta), std::domain_error);
+  EXPECT_THROW(normal_id_glm_lpdf(yn, x_bad, alpha, beta, 1.0), std::domain_error);
+  // messages agree with the reference body on the lazy path
+  std::string m_gpu, m_cpu;
+  try {
+    poisson_log_glm_lpmf(y, x_bad, alpha, beta);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    stan::math::poisson_log_glm_lpmf_reference_cpu(y, x_bad, alpha, beta);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+}
+
+TEST(CudaNormalLpdf, vectorised_matches_reference_loop) {
+  const int n = 100000;
+  Problem p = make_problem(n, 1, 5);
+  vector_v mu = to_v(0.1 * p.y_norm), sigma_v = to_v(p.sigma_vec), y_v = to_v(p.y_norm);
+  var sigma = 1.3;
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("normal_lpdf vec mu", normal_lpdf(p.y_norm, mu, sigma),
+                   normal_lpdf_reference_cpu(p.y_norm, mu, sigma), adj(mu), VectorXd::Constant(1, sigma.adj()));
+  STAN_CUDA_PARITY("normal_lpdf propto", normal_lpdf<true>(p.y_norm, mu, sigma),
+                   normal_lpdf_reference_cpu<true>(p.y_norm, mu, sigma), adj(mu),
+                   VectorXd::Constant(1, sigma.adj()));
+  STAN_CUDA_PARITY("normal_lpdf all var vectors", normal_lpdf(y_v, mu, sigma_v),
+                   normal_lpdf_reference_cpu(y_v, mu, sigma_v), adj(mu), adj(sigma_v), adj(y_v));
+  var mu0 = 0.25;
+  STAN_CUDA_PARITY("normal_lpdf scalar mu", normal_lpdf(p.y_norm, mu0, sigma),
+                   normal_lpdf_reference_cpu(p.y_norm, mu0, sigma), VectorXd::Constant(1, mu0.adj()),
+                   VectorXd::Constant(1, sigma.adj()));
+  // known answers of test/prob/normal/normal_test.hpp:11-40 through the vectorised entry
+  std::vector<double> y1{-3.5}, m1{1.9}, s1{7.2};
+  EXPECT_NEAR(-3.174269559226682080322, normal_lpdf(y1, m1, s1), 1e-14);
+  stan::math::recover_memory();
+}
+
+// --- map_rect: shards dispatched to devices ------------------------------------------------------
+struct glm_shard {
+  template <typename T1, typename T2>
+  Eigen::Matrix<typename stan::return_type<T1, T2>::type, Dynamic, 1> operator()(
+      const Matrix<T1, Dynamic, 1>& shared, const Matrix<T2, Dynamic, 1>& job, const std::vector<double>& x_r,
+      const std::vector<int>& x_i, std::ostream* msgs = 0) const {
+    typedef typename stan::return_type<T1, T2>::type T;
+    const int rows = x_i[0], k = x_i[1];
+    MatrixXd x = Eigen::Map<const MatrixXd>(x_r.data(), rows, k);
+    std::vector<int> y(x_i.begin() + 2, x_i.end());
+    Matrix<T, Dynamic, 1> res(1);
+    res(0) = stan::math::bernoulli_logit_glm_lpmf(y, x, job(0), shared);
+    return res;
+  }
+};
+
+TEST(CudaMapRect, hierarchical_logistic_matches_direct_sum) {
+  const int J = 12, rows = 3000, k = 32;
+  Problem p = make_problem(J * rows, k, 77);
+  std::vector<std::vector<double>> x_r(J);
+  std::vector<std::vector<int>> x_i(J);
+  for (int j = 0; j < J; ++j) {
+    MatrixXd xs = p.x.middleRows(j * rows, rows);
+    x_r[j].assign(xs.data(), xs.data() + xs.size());
+    x_i[j] = {rows, k};
+    x_i[j].insert(x_i[j].end(), p.y_bern.begin() + j * rows, p.y_bern.begin() + (j + 1) * rows);
+  }
+  for (int rep = 0; rep < 2; ++rep) {  // second pass hits the (call_id, job) cache
+    vector_v beta = to_v(p.beta);
+    std::vector<vector_v> job(J, vector_v(1));
+    for (int j = 0; j < J; ++j) job[j][0] = 0.01 * j;
+    vector_v out = stan::math::map_rect<3, glm_shard>(beta, job, x_r, x_i);
+    var total = stan::math::sum(out);
+    total.grad();
+    const double v = total.val();
+    VectorXd g = adj(beta);
+    VectorXd ga(J);
+    for (int j = 0; j < J; ++j) ga[j] = job[j][0].adj();
+    stan::math::set_zero_all_adjoints();
+    var ref = 0;
+    for (int j = 0; j < J; ++j) {
+      MatrixXd xs = p.x.middleRows(j * rows, rows);
+      std::vector<int> ys(p.y_bern.begin() + j * rows, p.y_bern.begin() + (j + 1) * rows);
+      ref += stan::math::bernoulli_logit_glm_lpmf_reference_cpu(ys, xs, job[j][0], beta);
+    }
+    ref.grad();
+    expect_rel(v, ref.val(), std::fabs(ref.val()), "map_rect value");
+    expect_vec(g, adj(beta), "map_rect shared grad");
+    VectorXd ga_ref(J);
+    for (int j = 0; j < J; ++j) ga_ref[j] = job[j][0].adj();
+    expect_vec(ga, ga_ref, "map_rect job grad");
+    stan::math::recover_memory();
+  }
+  stan_cuda_stats_t st;
+  stan_cuda_stats(&st);
+  EXPECT_GE(st.cache_hits, static_cast<uint64_t>(J));
+}
+#endif
