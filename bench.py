@@ -251,9 +251,8 @@ def main():
         glm.comm_init_from_torch(dist)
 
     # ---- this rank's rows --------------------------------------------------------------------
-    per = (n + world - 1) // world
-    r0 = rank * per
-    rows = max(0, min(per, n - r0))
+    from math_b200.shard import rank_rows
+    r0, rows = rank_rows(n, world, rank)
     x, y, alpha, beta, sigma = synth_shard(family, rows, k, seed=1000 + rank)
     fam = FAM_ID[family]
     flags = glm.glm_flags(fam, False)

@@ -182,7 +182,7 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
 int make_data_block(int device, int family, int64_t n_rows, int64_t k, const double* x, int64_t ldx,
                     int x_row_major, const void* y, int y_is_double, int64_t row0, cudaStream_t stream,
                     stan_cuda_data** out) {
-  if (n_rows <= 0 || k < 0 || !x || !y) return fail(STAN_CUDA_ERR_ARG, "data block: bad shape or null pointer");
+  if (n_rows <= 0 || k < 0 || (!x && k > 0) || !y) return fail(STAN_CUDA_ERR_ARG, "data block: bad shape or null pointer");
   if (family < 0 || family > 2) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
   stan_cuda_data* d = new stan_cuda_data();
   d->device = device;
