@@ -30,6 +30,12 @@
  *    1  STAN_CUDA_NONFINITE   the evaluation ran but its result is not finite; outputs are written;
  *                             the C++ wrapper then runs the reference's lazy check_finite sequence so
  *                             the same std::domain_error is thrown (bernoulli_logit_glm_lpmf.hpp:106-110)
+ *    2  STAN_CUDA_BAD_OUTCOME the device-resident outcome vector violates the family's domain (bernoulli:
+ *                             outside [0, 1], bernoulli_logit_glm_lpmf.hpp:70; poisson: negative,
+ *                             poisson_log_glm_lpmf.hpp:70).  The range of y is computed ONCE, on the device,
+ *                             when y is cached (the data is immutable), so the per-call O(N) host loop of
+ *                             check_bounded / check_nonnegative disappears; nothing was evaluated; the C++
+ *                             wrapper runs the reference's own check to throw the same std::domain_error
  *   <0  failure (bad argument, CUDA or NCCL error); stan_cuda_last_error() has the text;
  *       the C++ wrapper throws std::system_error (cf. stan/math/opencl/err/check_opencl.hpp)
  *
@@ -54,6 +60,7 @@ extern "C" {
 
 #define STAN_CUDA_OK 0
 #define STAN_CUDA_NONFINITE 1
+#define STAN_CUDA_BAD_OUTCOME 2
 #define STAN_CUDA_ERR_ARG (-1)
 #define STAN_CUDA_ERR_CUDA (-2)
 #define STAN_CUDA_ERR_NCCL (-3)
@@ -186,6 +193,8 @@ STAN_CUDA_API int64_t stan_cuda_data_params_len(stan_cuda_data_t d); /* = k_pad 
 STAN_CUDA_API int64_t stan_cuda_data_result_len(stan_cuda_data_t d); /* = k_pad + 4: [lp, sum_d, sum_s2, status, dbeta(k_pad)] */
 STAN_CUDA_API int64_t stan_cuda_data_kpad(stan_cuda_data_t d);
 STAN_CUDA_API int64_t stan_cuda_data_algorithmic_bytes(stan_cuda_data_t d); /* n*k*8 + n*sizeof(y) */
+/* Smallest / largest integer outcome seen at fill (0, 0 for real outcomes). */
+STAN_CUDA_API int stan_cuda_data_y_range(stan_cuda_data_t d, int64_t* y_min, int64_t* y_max);
 /* Enqueue one fused evaluation on `stream` (a cudaStream_t).  d_params / d_result are device
  * pointers (layouts above); d_alpha_vec, d_sigma_vec, d_row_out may be NULL (scalar alpha/sigma,
  * no per-row outputs).  No host synchronisation, no copies. */

@@ -6,7 +6,7 @@ that identical argument blocks can be handed to the CUDA library and to the CPU 
 """
 import ctypes as C
 
-OK, NONFINITE = 0, 1
+OK, NONFINITE, BAD_OUTCOME = 0, 1, 2
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
 
 BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID = 0, 1, 2
@@ -106,6 +106,7 @@ PROTOTYPES = {
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "stan_cuda_allreduce": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p]),
     "stan_cuda_data_launches_per_eval": (C.c_int, [C.c_void_p]),
+    "stan_cuda_data_y_range": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
 }
 
 

@@ -30,10 +30,13 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    """Compile every .cu into an object (parallel) and link the shared library."""
+def build(force=False, verbose=False, variant="", extra_flags=()):
+    """Compile every .cu into an object (parallel) and link the shared library.  `variant` names a
+    debugging build (e.g. "timers" with -DSTAN_CUDA_PHASE_TIMERS, used by tools/phase_timers.py);
+    it goes to libstanmath_cuda_<variant>.so and never replaces the product library."""
     os.makedirs(LIB_DIR, exist_ok=True)
-    obj_dir = os.path.join(LIB_DIR, "obj")
+    LIB = os.path.join(LIB_DIR, "libstanmath_cuda%s.so" % ("_" + variant if variant else ""))
+    obj_dir = os.path.join(LIB_DIR, "obj" + ("_" + variant if variant else ""))
     os.makedirs(obj_dir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     headers.append(os.path.join(ROOT, "include", "stan_cuda.h"))
@@ -43,7 +46,7 @@ def build(force=False, verbose=False):
         o = os.path.join(obj_dir, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _stale(o, [s] + headers):
-            cmd = [nvcc()] + NVCC_FLAGS + ["-c", s, "-o", o]
+            cmd = [nvcc()] + NVCC_FLAGS + list(extra_flags) + ["-c", s, "-o", o]
             if verbose:
                 print(" ".join(cmd))
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))

@@ -10,6 +10,7 @@
 // (stan/math/prim/mat/functor/mpi_parallel_call.hpp:40-89).
 #include <math.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <map>
@@ -191,6 +192,16 @@ int glm_eval(const stan_cuda_glm_args* a) {
   std::shared_ptr<Entry> e;
   SC_TRY(get_glm_entry(a, &e));
   const size_t S = e->shards.size();
+  // eager domain check of the outcomes (bernoulli_logit_glm_lpmf.hpp:70, poisson_log_glm_lpmf.hpp:70)
+  // from the range computed at fill: no O(N) host loop per call
+  if (a->family != STAN_CUDA_NORMAL_ID) {
+    int64_t lo = e->shards[0].d->y_min, hi = e->shards[0].d->y_max;
+    for (size_t s = 1; s < S; ++s) {
+      lo = std::min(lo, e->shards[s].d->y_min);
+      hi = std::max(hi, e->shards[s].d->y_max);
+    }
+    if (lo < 0 || (a->family == STAN_CUDA_BERNOULLI_LOGIT && hi > 1)) return STAN_CUDA_BAD_OUTCOME;
+  }
   const bool alpha_vec = a->alpha_len != 1;
   const bool sigma_vec = a->family == STAN_CUDA_NORMAL_ID && a->sigma_len != 1;
   const bool want_rowa = ((a->flags & STAN_CUDA_NEED_DALPHA) && alpha_vec && a->dalpha) ||

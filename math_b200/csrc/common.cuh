@@ -71,6 +71,7 @@ struct stan_cuda_data {
   double* x = nullptr;   // tiled layout, zero padded
   void* y = nullptr;     // int32 or double, padded to tiles * R
   double lgamma_sum = 0; // sum lgamma(y+1) (poisson), computed once at fill
+  int64_t y_min = 0, y_max = 0;  // range of the integer outcomes, computed once at fill
   size_t bytes = 0;
   stancuda::Workspace ws;  // used by the device-level API (stan_cuda_glm_launch)
 };

@@ -5,6 +5,7 @@
 // R rows x kpad columns, column-major inside the tile (see common.cuh / DESIGN.md).  The host
 // matrix (Eigen column-major, or row-major) is streamed through a bounded staging buffer and
 // re-tiled by a kernel, so the fill never needs a second full-size copy of X on the device.
+#include <limits.h>
 #include <math.h>
 
 #include <chrono>
@@ -47,20 +48,41 @@ __global__ void retile_rowmajor_kernel(const double* __restrict__ src, int64_t s
   }
 }
 
-// sum lgamma(y + 1) over int y: per-block partials in block order, summed on the host in order
-// (poisson_log_glm_lpmf.hpp:102-108 -- depends on data only, so it is computed once per fill).
-__global__ void lgamma_partial_kernel(const int* __restrict__ y, int64_t n, double* __restrict__ partial) {
+// Statistics of the integer outcomes, computed once per fill (the data is immutable):
+//   min / max   -> the eager domain checks check_bounded(y, 0, 1) / check_nonnegative(y)
+//                  (bernoulli_logit_glm_lpmf.hpp:70, poisson_log_glm_lpmf.hpp:70) without a per-call
+//                  O(N) host loop;
+//   sum lgamma(y + 1) (poisson_log_glm_lpmf.hpp:102-108), depends on data only.
+// Per-block partials in block order, combined on the host in order.
+__global__ void y_stats_kernel(const int* __restrict__ y, int64_t n, int want_lgamma, double* __restrict__ partial,
+                               int* __restrict__ minmax) {
   __shared__ double sh[256];
+  __shared__ int smin[256], smax[256];
   double s = 0.0;
-  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
-    s += lgamma(double(y[i]) + 1.0);
+  int lo = INT_MAX, hi = INT_MIN;
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+    const int v = y[i];
+    lo = v < lo ? v : lo;
+    hi = v > hi ? v : hi;
+    if (want_lgamma) s += v >= 0 ? lgamma(double(v) + 1.0) : 0.0;
+  }
   sh[threadIdx.x] = s;
+  smin[threadIdx.x] = lo;
+  smax[threadIdx.x] = hi;
   __syncthreads();
   for (int off = 128; off > 0; off >>= 1) {
-    if (int(threadIdx.x) < off) sh[threadIdx.x] += sh[threadIdx.x + off];
+    if (int(threadIdx.x) < off) {
+      sh[threadIdx.x] += sh[threadIdx.x + off];
+      smin[threadIdx.x] = min(smin[threadIdx.x], smin[threadIdx.x + off]);
+      smax[threadIdx.x] = max(smax[threadIdx.x], smax[threadIdx.x + off]);
+    }
     __syncthreads();
   }
-  if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+  if (threadIdx.x == 0) {
+    partial[blockIdx.x] = sh[0];
+    minmax[2 * blockIdx.x] = smin[0];
+    minmax[2 * blockIdx.x + 1] = smax[0];
+  }
 }
 
 static const size_t kStageBytes = size_t(256) << 20;  // staging buffer for the fill
@@ -158,19 +180,32 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
   counters().launches.fetch_add(1, std::memory_order_relaxed);
 
   d->lgamma_sum = 0.0;
-  if (d->family == STAN_CUDA_POISSON_LOG && !d->y_is_double) {
+  d->y_min = d->y_max = 0;
+  if (!d->y_is_double) {
     const int nb = 256;
-    double* partial = nullptr;
-    SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&partial), nb * sizeof(double)));
-    lgamma_partial_kernel<<<nb, 256, 0, stream>>>(static_cast<const int*>(d->y), n, partial);
+    double* partial = nullptr;  // [nb] doubles followed by [2 * nb] ints
+    SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&partial), nb * (sizeof(double) + 2 * sizeof(int))));
+    int* mm = reinterpret_cast<int*>(partial + nb);
+    y_stats_kernel<<<nb, 256, 0, stream>>>(static_cast<const int*>(d->y), n, d->family == STAN_CUDA_POISSON_LOG,
+                                           partial, mm);
     double host[256];
+    int hmm[512];
     cudaError_t e = cudaMemcpyAsync(host, partial, sizeof(host), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(hmm, mm, sizeof(hmm), cudaMemcpyDeviceToHost, stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
     cudaFree(partial);
     SC_CUDA_CLEAN(e);
     double s = 0.0;
-    for (int i = 0; i < nb; ++i) s += host[i];
+    int lo = INT_MAX, hi = INT_MIN;
+    for (int i = 0; i < nb; ++i) {
+      s += host[i];
+      lo = hmm[2 * i] < lo ? hmm[2 * i] : lo;
+      hi = hmm[2 * i + 1] > hi ? hmm[2 * i + 1] : hi;
+    }
     d->lgamma_sum = s;
+    d->y_min = lo;
+    d->y_max = hi;
+    counters().launches.fetch_add(1, std::memory_order_relaxed);
   }
   SC_CUDA_CLEAN(cudaStreamSynchronize(stream));
 #undef SC_CUDA_CLEAN
@@ -250,6 +285,12 @@ int64_t stan_cuda_data_algorithmic_bytes(stan_cuda_data_t d) {
   return d->n * d->k * int64_t(sizeof(double)) + d->n * int64_t(d->y_is_double ? sizeof(double) : sizeof(int));
 }
 int stan_cuda_data_launches_per_eval(stan_cuda_data_t d) { return d ? 1 : 0; }
+int stan_cuda_data_y_range(stan_cuda_data_t d, int64_t* y_min, int64_t* y_max) {
+  if (!d) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_data_y_range: null handle");
+  if (y_min) *y_min = d->y_min;
+  if (y_max) *y_max = d->y_max;
+  return STAN_CUDA_OK;
+}
 
 int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params, const double* d_alpha_vec,
                          const double* d_sigma_vec, double* d_result, double* d_row_dalpha,

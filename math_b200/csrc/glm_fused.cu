@@ -49,11 +49,24 @@ struct GlmKernelParams {
   double* result;
   uint32_t flags;
   double lgamma_sum;
+#ifdef STAN_CUDA_PHASE_TIMERS
+  unsigned long long* timers;  // [grid][4] globaltimer stamps: start, first tile landed, loop end, CTA partial written; [grid*4] = end of last CTA
+#endif
 };
 
 // ---------------------------------------------------------------------------------------------
 // PTX helpers: mbarrier + 1-D TMA bulk copy (SASS: UBLKCP / SYNCS)
 // ---------------------------------------------------------------------------------------------
+#ifdef STAN_CUDA_PHASE_TIMERS
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define PHASE_STAMP(slot) do { if (tid == 0 && p.timers) p.timers[size_t(blockIdx.x) * 4 + (slot)] = gtimer(); } while (0)
+#else
+#define PHASE_STAMP(slot) do { } while (0)
+#endif
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
@@ -183,6 +196,7 @@ glm_fused_kernel(const GlmKernelParams p) {
     tma_bulk_g2s(dst + p.tile_bytes, ybytes + tile * p.y_bytes, p.y_bytes, bar, policy);
   };
 
+  PHASE_STAMP(0);
   if (tid == 0) {
     for (int s = 0; s < p.stages; ++s) mbar_init(smem_u32(&bars[s]), 1);
     mbar_fence_init();
@@ -213,6 +227,9 @@ glm_fused_kernel(const GlmKernelParams p) {
     const int64_t tile = int64_t(blockIdx.x) + int64_t(it) * grid;
     const int64_t row = tile * R + r;
     mbar_wait(smem_u32(&bars[s]), parity);
+#ifdef STAN_CUDA_PHASE_TIMERS
+    if (it == 0) PHASE_STAMP(1);
+#endif
 
     const unsigned char* st = stage0 + size_t(s) * p.stage_bytes;
     const double* xs = reinterpret_cast<const double*>(st) + (cg * kc) * R + r;
@@ -273,6 +290,7 @@ glm_fused_kernel(const GlmKernelParams p) {
     for (int j = 0; j < kMaxKc; ++j) acc[j] = fma(xr[j], d, acc[j]);
   }
 
+  PHASE_STAMP(2);
   // ---- CTA reduction: lanes of a column group -> warps of a column group -> CTA partial -----
   const int width = R < 32 ? R : 32;
   const int lane = tid & 31, warp = tid >> 5;
@@ -313,6 +331,7 @@ glm_fused_kernel(const GlmKernelParams p) {
   // ---- last CTA adds the CTA partials in CTA order --------------------------------------------
   __threadfence();
   __syncthreads();
+  PHASE_STAMP(3);
   if (tid == 0) {
     const unsigned int t = atomicAdd(p.ticket, 1u);
     s_is_last = (t == unsigned(grid) - 1u);
@@ -360,6 +379,9 @@ glm_fused_kernel(const GlmKernelParams p) {
     p.result[2] = dsig;
     p.result[3] = witness;
     *p.ticket = 0u;  // ready for the next launch on this workspace (stream ordered)
+#ifdef STAN_CUDA_PHASE_TIMERS
+    if (p.timers) p.timers[size_t(grid) * 4] = gtimer();
+#endif
   }
 }
 
@@ -461,6 +483,10 @@ static size_t smem_bytes(const Tiling& t, int stages, size_t* stage_bytes_out) {
   return size_t(stages) * stage + fixed;
 }
 
+#ifdef STAN_CUDA_PHASE_TIMERS
+static unsigned long long* g_phase_timers = nullptr;  // debugging build only (tools/phase_timers.py)
+#endif
+
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
@@ -506,6 +532,9 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
   p.result = io.d_result;
   p.flags = io.flags;
   p.lgamma_sum = d->lgamma_sum;
+#ifdef STAN_CUDA_PHASE_TIMERS
+  p.timers = g_phase_timers;
+#endif
   const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
   switch (d->family) {
     case STAN_CUDA_BERNOULLI_LOGIT:
@@ -519,6 +548,12 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
 }
 
 }  // namespace stancuda
+
+#ifdef STAN_CUDA_PHASE_TIMERS
+extern "C" STAN_CUDA_API void stan_cuda_debug_set_timers(unsigned long long* device_buf) {
+  stancuda::g_phase_timers = device_buf;
+}
+#endif
 
 extern "C" void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm) {
   stancuda::Tuning& t = stancuda::tuning_mut();

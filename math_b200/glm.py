@@ -188,13 +188,15 @@ def _glm(function, fam, y, x, alpha, beta, sigma, propto, need_dy=False):
     if sg is not None:
         _size_check(function, "Vector of scale parameters", sg, n)
     _size_check(function, "Vector of intercepts", al, n)
-    if fam == _abi.BERNOULLI_LOGIT and ya.size and not np.all((ya >= 0) & (ya <= 1)):   # check_bounded, :70
-        raise DomainError("%s: Vector of dependent variables must be in the interval [0, 1]" % function)
-    if fam == _abi.POISSON_LOG and ya.size and not np.all(ya >= 0):                     # check_nonnegative, :70
-        raise DomainError("%s: Vector of dependent variables must be >= 0" % function)
     if n == 0 or (fam == _abi.NORMAL_ID and sg.size == 0):
         return 0.0, {}
     r = glm_eval(fam, ya, xa, al, be, sg, propto=propto, need_dy=need_dy)
+    if r["rc"] == _abi.BAD_OUTCOME:
+        # check_bounded / check_nonnegative (:70): answered by the device from the range of y computed
+        # once at cache fill; the host loop runs only here, to word the exception
+        if fam == _abi.BERNOULLI_LOGIT:
+            raise DomainError("%s: Vector of dependent variables must be in the interval [0, 1]" % function)
+        raise DomainError("%s: Vector of dependent variables must be >= 0" % function)
     _lazy_finite_checks(function, fam, r["rc"], xa, ya, al, be, sg)
     grads = {"beta": r["dbeta"], "alpha": r["dalpha"]}
     if fam == _abi.NORMAL_ID:

@@ -32,11 +32,13 @@ return_type_t<T_x, T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y
   if (is_vector<T_alpha>::value) {
     check_consistent_sizes(function, "Vector of intercepts", alpha, "Vector of dependent variables", y);
   }
-  check_bounded(function, "Vector of dependent variables", y, 0, 1);
+  // check_bounded(y, 0, 1) (:70) is answered by the device from the range computed when y was
+  // cached -- no O(N) host loop per evaluation; see STAN_CUDA_BAD_OUTCOME below.
   if (size_zero(y)) {
     return 0;
   }
   if (!include_summand<propto, T_x, T_alpha, T_beta>::value) {
+    check_bounded(function, "Vector of dependent variables", y, 0, 1);  // nothing goes to the device
     return 0;
   }
 
@@ -55,7 +57,12 @@ return_type_t<T_x, T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y
     a.flags |= STAN_CUDA_NEED_DALPHA;
     a.dalpha = partials_data(ops_partials.edge2_);
   }
-  if (!call.run(function)) {
+  int rc = call.run(function);
+  if (rc == STAN_CUDA_BAD_OUTCOME) {
+    check_bounded(function, "Vector of dependent variables", y, 0, 1);  // throws as the reference does
+    rc = call.rerun_after_stale_outcomes(function);
+  }
+  if (rc == STAN_CUDA_NONFINITE) {
     check_finite(function, "Weight vector", beta);
     check_finite(function, "Intercept", alpha);
     Eigen::Array<double, Eigen::Dynamic, 1> ytheta = call.host_linear_predictor(x).array();

@@ -5,6 +5,8 @@
 #include <stan/math/cuda/c_api.h>
 #include <stan/math/cuda/err.hpp>
 #include <stan/math/cuda/marshal.hpp>
+#include <string>
+#include <system_error>
 #include <vector>
 
 namespace stan {
@@ -48,11 +50,32 @@ class glm_call {
   const double* beta_data() const { return a_.beta; }
   const double* alpha_data() const { return a_.alpha; }
 
-  /** Runs the evaluation; returns true when the result is finite. */
-  bool run(const char* function) {
+  /**
+   * Runs the evaluation.  Returns STAN_CUDA_OK, STAN_CUDA_NONFINITE (outputs written, the caller
+   * runs the reference's lazy check_finite sequence) or STAN_CUDA_BAD_OUTCOME (the device-resident
+   * outcomes violate the family's domain; nothing evaluated; the caller runs the reference's eager
+   * outcome check, which throws).  Failures of the device layer throw std::system_error.
+   */
+  int run(const char* function) {
     const int rc = stan_cuda_glm_eval(&a_);
     check_cuda_rc(function, rc);
-    return rc != STAN_CUDA_NONFINITE;
+    return rc;
+  }
+
+  /**
+   * The device said the outcomes are out of range but the reference's host check (run by the
+   * caller just before this) accepted them: the device copy is stale (host y was rewritten in
+   * place).  Drop it, refill from the host data and evaluate again.
+   */
+  int rerun_after_stale_outcomes(const char* function) {
+    stan_cuda_cache_invalidate(a_.y);
+    stan_cuda_cache_invalidate(a_.x);
+    const int rc = run(function);
+    if (rc == STAN_CUDA_BAD_OUTCOME) {
+      throw std::system_error(STAN_CUDA_ERR_STATE, std::generic_category(),
+                              std::string(function) + ": device copy of the outcome vector disagrees with the host");
+    }
+    return rc;
   }
 
   /** Host recomputation of X * beta + alpha, used only on the error path so that the reference's

@@ -78,7 +78,7 @@ return_type_t<T_y, T_x, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(cons
     a.flags |= STAN_CUDA_NEED_DSIGMA;
     a.dsigma = partials_data(ops_partials.edge5_);
   }
-  if (!call.run(function)) {
+  if (call.run(function) == STAN_CUDA_NONFINITE) {
     const double y_scaled_sq_sum = call.witness();
     check_finite(function, "Vector of dependent variables", y);
     check_finite(function, "Weight vector", beta);

@@ -32,11 +32,13 @@ return_type_t<T_x, T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, co
   if (is_vector<T_alpha>::value) {
     check_consistent_sizes(function, "Vector of intercepts", alpha, "Vector of dependent variables", y);
   }
-  check_nonnegative(function, "Vector of dependent variables", y);
+  // check_nonnegative(y) (:70) is answered by the device from the range computed when y was
+  // cached -- no O(N) host loop per evaluation; see STAN_CUDA_BAD_OUTCOME below.
   if (size_zero(y)) {
     return 0;
   }
   if (!include_summand<propto, T_x, T_alpha, T_beta>::value) {
+    check_nonnegative(function, "Vector of dependent variables", y);  // nothing goes to the device
     return 0;
   }
 
@@ -61,7 +63,12 @@ return_type_t<T_x, T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, co
     a.flags |= STAN_CUDA_NEED_DALPHA;
     a.dalpha = partials_data(ops_partials.edge2_);
   }
-  if (!call.run(function)) {
+  int rc = call.run(function);
+  if (rc == STAN_CUDA_BAD_OUTCOME) {
+    check_nonnegative(function, "Vector of dependent variables", y);  // throws as the reference does
+    rc = call.rerun_after_stale_outcomes(function);
+  }
+  if (rc == STAN_CUDA_NONFINITE) {
     check_finite(function, "Weight vector", beta);
     check_finite(function, "Intercept", alpha);
     Eigen::Matrix<double, Eigen::Dynamic, 1> theta = call.host_linear_predictor(x);

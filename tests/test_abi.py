@@ -69,13 +69,10 @@ def test_fails_loudly_without_gpu(cdll):
 
 
 def test_host_wrapper_error_contract_without_device():
-    """Eager checks run before the ABI call, exactly where the reference has them."""
+    """Eager parameter and size checks run before the ABI call, exactly where the reference has
+    them (the outcome range check is answered by the device: tests/test_glm_gpu.py)."""
     from math_b200 import glm
     x = np.ones((3, 2))
-    with pytest.raises(glm.DomainError):
-        glm.bernoulli_logit_glm_lpmf([1, 0, 23], x, 0.3, [0.1, 0.2])
-    with pytest.raises(glm.DomainError):
-        glm.poisson_log_glm_lpmf([1, 0, -1], x, 0.3, [0.1, 0.2])
     with pytest.raises(glm.DomainError):
         glm.normal_id_glm_lpdf([1.0, 0.0, 2.0], x, 0.3, [0.1, 0.2], [0.0])
     with pytest.raises(ValueError):

@@ -134,6 +134,33 @@ def test_error_contract_lazy_checks(glm):
     assert np.isnan(lp)
 
 
+def test_outcome_domain_is_checked_on_the_device_at_fill(glm):
+    """check_bounded(y, 0, 1) / check_nonnegative(y) (bernoulli/poisson :70): the range of y is
+    computed once when y is cached; the call reports BAD_OUTCOME and the wrapper raises the
+    reference's domain error -- no O(N) host loop per evaluation."""
+    x = np.ones((3, 2))
+    with pytest.raises(glm.DomainError, match="interval"):
+        glm.bernoulli_logit_glm_lpmf([1, 0, 23], x, 0.3, [0.1, 0.2])
+    with pytest.raises(glm.DomainError, match=">= 0"):
+        glm.poisson_log_glm_lpmf([1, 0, -1], x, 0.3, [0.1, 0.2])
+    # outcome errors win over parameter errors, as in the reference (eager before lazy)
+    with pytest.raises(glm.DomainError, match=">= 0"):
+        glm.poisson_log_glm_lpmf([1, 0, -1], x, 0.3, [0.1, np.inf])
+    s = synth_glm("poisson_log", 50000, 8, seed=5)
+    y = s["y"].copy()
+    y[31337] = -4
+    r = glm.glm_eval("poisson_log", y, s["x"], s["alpha"], s["beta"])
+    assert r["rc"] == _abi.BAD_OUTCOME
+    d = glm.GlmData("bernoulli_logit", s["x"], np.minimum(s["y"], 1))
+    import ctypes
+    lo, hi = ctypes.c_int64(), ctypes.c_int64()
+    from math_b200._lib import lib
+    assert lib().stan_cuda_data_y_range(d.h, ctypes.byref(lo), ctypes.byref(hi)) == 0
+    assert (lo.value, hi.value) == (0, 1)
+    d.close()
+    glm.cache_clear()
+
+
 def test_device_cache_hit_refill_and_invalidate(glm):
     s = synth_glm("poisson_log", 20000, 24, seed=1)
     glm.cache_clear()
