@@ -212,6 +212,25 @@ struct shard_functor {
   }
 };
 
+// The same shard with x passed as a zero-copy view of x_r (cuda::data_matrix_view, an extension of
+// the CUDA subsystem): no per-call copy of the design matrix on the host.
+struct shard_functor_view {
+  template <typename T1, typename T2>
+  Matrix<typename stan::return_type<T1, T2>::type, Dynamic, 1> operator()(
+      const Matrix<T1, Dynamic, 1>& shared, const Matrix<T2, Dynamic, 1>& job, const std::vector<double>& x_r,
+      const std::vector<int>& x_i, std::ostream* msgs = 0) const {
+    typedef typename stan::return_type<T1, T2>::type T;
+    const int rows = x_i[0], k = x_i[1];
+    stan::math::cuda::data_matrix_view x(x_r.data(), rows, k);
+    Eigen::Map<const Matrix<int, Dynamic, 1>> y_map(x_i.data() + 2, rows);
+    Matrix<int, Dynamic, 1> y = y_map;
+    Matrix<T, Dynamic, 1> res(1);
+    T2 alpha = job[0];
+    res(0) = stan::math::bernoulli_logit_glm_lpmf(y, x, alpha, shared);
+    return res;
+  }
+};
+
 struct ShardSet {
   std::vector<std::vector<double>> x_r;
   std::vector<std::vector<int>> x_i;
@@ -263,6 +282,8 @@ double map_rect_once(const Problem& p, const ShardSet& s, Result* out) {
   vector_v res;
   if (MODE == 0) {
     res = map_rect<CALL_ID, shard_functor<true, FAMILY, SHARED_ALPHA>>(shared, job, s.x_r, s.x_i);
+  } else if (MODE == 2) {
+    res = map_rect<CALL_ID + 200, shard_functor_view>(shared, job, s.x_r, s.x_i);
   } else {
     res = internal::map_rect_concurrent_reference_cpu<CALL_ID + 100, shard_functor<false, FAMILY, SHARED_ALPHA>>(
         shared, job, s.x_r, s.x_i, nullptr);
@@ -404,7 +425,12 @@ int run(int argc, char** argv) {
       map_rect_once<0, 0, false, 5>(p, s, &g);  // cache fill
       Timing tg = time_reps(3, reps, 60, [&] { return map_rect_once<0, 0, false, 5>(p, s, &g); });
       print_timing("gpu_map_rect", tg);
+      Result gv;
+      map_rect_once<2, 0, false, 5>(p, s, &gv);
+      Timing tv = time_reps(3, reps, 60, [&] { return map_rect_once<2, 0, false, 5>(p, s, &gv); });
       std::printf(", ");
+      print_timing("gpu_map_rect_zero_copy_view", tv);
+      std::printf(", \"view_vs_copy_rel_err\": %.3e, ", rel_err(gv, g));
     }
     if (!no_cpu) {
       Timing tc = time_reps(1, cpu_reps, 60, [&] { return map_rect_once<1, 0, false, 5>(p, s, &c); });

@@ -36,6 +36,7 @@ struct GlmKernelParams {
   int R, C, kc, kpad;
   int log2R;
   int stages;
+  int group_size;        // CTAs per reduction group (two-level final sum)
   uint32_t stage_bytes;  // per stage in shared memory (tile + y, 128-aligned)
   uint32_t tile_bytes;
   uint32_t y_bytes;      // per tile
@@ -328,13 +329,43 @@ glm_fused_kernel(const GlmKernelParams p) {
     my_scratch[c] = sum;
   }
 
-  // ---- last CTA adds the CTA partials in CTA order --------------------------------------------
+  // ---- two-level fixed-order reduction of the CTA partials -----------------------------------
+  // CTAs are grouped in blocks of `gsz` consecutive CTAs.  The last CTA of a group to finish adds
+  // the group's partials in CTA order; the last group to finish adds the group sums in group
+  // order.  The grouping depends on the grid only, so the result is bit-reproducible, and the
+  // critical path after the slowest CTA is two short (<= ~25 term) sums instead of one of `grid`.
   __threadfence();
   __syncthreads();
   PHASE_STAMP(3);
+  const int gsz = p.group_size, ngroups = (grid + gsz - 1) / gsz;
+  const int g = int(blockIdx.x) / gsz;
+  const int gfirst = g * gsz, glast = (gfirst + gsz < grid) ? gfirst + gsz : grid;
   if (tid == 0) {
+    const unsigned int t = atomicAdd(p.ticket + 1 + g, 1u);
+    s_is_last = (t == unsigned(glast - gfirst) - 1u);
+  }
+  __syncthreads();
+  if (!s_is_last) return;
+  __threadfence();
+  double* gscratch = p.scratch + size_t(grid) * cols;  // [ngroups][cols]
+  for (int c = tid; c < cols; c += THREADS) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int b = gfirst;
+    for (; b + 4 <= glast; b += 4) {
+      s0 += __ldcg(p.scratch + size_t(b + 0) * cols + c);
+      s1 += __ldcg(p.scratch + size_t(b + 1) * cols + c);
+      s2 += __ldcg(p.scratch + size_t(b + 2) * cols + c);
+      s3 += __ldcg(p.scratch + size_t(b + 3) * cols + c);
+    }
+    for (; b < glast; ++b) s0 += __ldcg(p.scratch + size_t(b) * cols + c);
+    gscratch[size_t(g) * cols + c] = (s0 + s1) + (s2 + s3);
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    p.ticket[1 + g] = 0u;  // every CTA of the group has taken its ticket: ready for the next launch
     const unsigned int t = atomicAdd(p.ticket, 1u);
-    s_is_last = (t == unsigned(grid) - 1u);
+    s_is_last = (t == unsigned(ngroups) - 1u);
   }
   __syncthreads();
   if (!s_is_last) return;
@@ -342,13 +373,13 @@ glm_fused_kernel(const GlmKernelParams p) {
   for (int c = tid; c < cols; c += THREADS) {
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
     int b = 0;
-    for (; b + 4 <= grid; b += 4) {
-      s0 += __ldcg(p.scratch + size_t(b + 0) * cols + c);
-      s1 += __ldcg(p.scratch + size_t(b + 1) * cols + c);
-      s2 += __ldcg(p.scratch + size_t(b + 2) * cols + c);
-      s3 += __ldcg(p.scratch + size_t(b + 3) * cols + c);
+    for (; b + 4 <= ngroups; b += 4) {
+      s0 += __ldcg(gscratch + size_t(b + 0) * cols + c);
+      s1 += __ldcg(gscratch + size_t(b + 1) * cols + c);
+      s2 += __ldcg(gscratch + size_t(b + 2) * cols + c);
+      s3 += __ldcg(gscratch + size_t(b + 3) * cols + c);
     }
-    for (; b < grid; ++b) s0 += __ldcg(p.scratch + size_t(b) * cols + c);
+    for (; b < ngroups; ++b) s0 += __ldcg(gscratch + size_t(b) * cols + c);
     const double tot = (s0 + s1) + (s2 + s3);
     if (c >= 4) p.result[c] = tot;
     else part[c] = tot;
@@ -508,7 +539,11 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
   int64_t grid64 = int64_t(sms) * ctas_per_sm;
   if (grid64 > t.tiles) grid64 = t.tiles;
   const int grid = int(grid64);
-  SC_TRY(workspace_reserve(ws, d->device, size_t(grid) * (t.kpad + 4)));
+  int group_size = 1;  // ~sqrt(grid): both levels of the final sum have about the same length
+  while (group_size * group_size < grid) ++group_size;
+  const int ngroups = (grid + group_size - 1) / group_size;  // <= 25 for grid <= 592 (ticket block holds 63)
+  if (ngroups > 60) return fail(STAN_CUDA_ERR_ARG, "launch_glm: grid too large for the ticket block");
+  SC_TRY(workspace_reserve(ws, d->device, size_t(grid + ngroups) * (t.kpad + 4)));
 
   GlmKernelParams p;
   p.x = d->x;
@@ -519,6 +554,7 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
   p.log2R = 0;
   while ((1 << p.log2R) < t.R) ++p.log2R;
   p.stages = stages;
+  p.group_size = group_size;
   p.stage_bytes = uint32_t(stage_bytes);
   p.tile_bytes = uint32_t(t.tile_bytes());
   p.y_bytes = uint32_t(size_t(t.R) * (d->y_is_double ? sizeof(double) : sizeof(int)));

@@ -55,6 +55,24 @@ inline return_type_t<T_y, T_x, T_alpha, T_beta, T_scale> normal_id_glm_lpdf(cons
   return normal_id_glm_lpdf<false>(y, x, alpha, beta, sigma);
 }
 
+#ifdef STAN_CUDA
+/** Extension of the CUDA subsystem: x as a zero-copy view of column-major data (cuda::data_matrix_view). */
+template <bool propto, typename T_y, typename T_alpha, typename T_beta, typename T_scale>
+inline return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf(const T_y& y, const cuda::data_matrix_view& x,
+                                                                       const T_alpha& alpha, const T_beta& beta,
+                                                                       const T_scale& sigma) {
+  static_assert(cuda::normal_glm_eligible<T_y, cuda::data_matrix_view, T_alpha, T_beta, T_scale>::value,
+                "a data_matrix_view is accepted on the device path only");
+  return cuda::normal_id_glm_lpdf_device<propto>(y, x, alpha, beta, sigma);
+}
+template <typename T_y, typename T_alpha, typename T_beta, typename T_scale>
+inline return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf(const T_y& y, const cuda::data_matrix_view& x,
+                                                                       const T_alpha& alpha, const T_beta& beta,
+                                                                       const T_scale& sigma) {
+  return cuda::normal_id_glm_lpdf_device<false>(y, x, alpha, beta, sigma);
+}
+#endif
+
 }  // namespace math
 }  // namespace stan
 #endif

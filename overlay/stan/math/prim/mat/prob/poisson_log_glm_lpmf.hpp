@@ -55,6 +55,22 @@ inline return_type_t<T_x, T_beta, T_alpha> poisson_log_glm_lpmf(const T_y& y, co
   return poisson_log_glm_lpmf<false>(y, x, alpha, beta);
 }
 
+#ifdef STAN_CUDA
+/** Extension of the CUDA subsystem: x as a zero-copy view of column-major data (cuda::data_matrix_view). */
+template <bool propto, typename T_y, typename T_alpha, typename T_beta>
+inline return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf(const T_y& y, const cuda::data_matrix_view& x, const T_alpha& alpha,
+                                         const T_beta& beta) {
+  static_assert(cuda::int_glm_eligible<T_y, cuda::data_matrix_view, T_alpha, T_beta>::value,
+                "a data_matrix_view is accepted on the device path only");
+  return cuda::poisson_log_glm_lpmf_device<propto>(y, x, alpha, beta);
+}
+template <typename T_y, typename T_alpha, typename T_beta>
+inline return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf(const T_y& y, const cuda::data_matrix_view& x, const T_alpha& alpha,
+                                         const T_beta& beta) {
+  return cuda::poisson_log_glm_lpmf_device<false>(y, x, alpha, beta);
+}
+#endif
+
 }  // namespace math
 }  // namespace stan
 #endif

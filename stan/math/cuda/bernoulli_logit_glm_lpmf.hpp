@@ -21,7 +21,7 @@ namespace cuda {
  * reports a non-finite log-density (:106-110).
  */
 template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta>
-return_type_t<T_x, T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y, const T_x& x,
+return_type_t<T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y, const T_x& x,
                                                                     const T_alpha& alpha, const T_beta& beta) {
   static const char* function = "bernoulli_logit_glm_lpmf";
   const size_t N = x.rows();
@@ -37,14 +37,16 @@ return_type_t<T_x, T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y
   if (size_zero(y)) {
     return 0;
   }
-  if (!include_summand<propto, T_x, T_alpha, T_beta>::value) {
+  if (!include_summand<propto, double, T_alpha, T_beta>::value) {
     check_bounded(function, "Vector of dependent variables", y, 0, 1);  // nothing goes to the device
     return 0;
   }
 
   int_outcome<T_y> y_val(y, N);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_BERNOULLI_LOGIT, x, alpha, beta);
-  operands_and_partials<T_x, T_alpha, T_beta> ops_partials(x, alpha, beta);
+  // x is data on this path: its (empty) edge is declared on a double so that views of x work too
+  const double x_placeholder = 0;
+  operands_and_partials<double, T_alpha, T_beta> ops_partials(x_placeholder, alpha, beta);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_is_double = 0;

@@ -28,6 +28,18 @@ struct is_data_matrix : std::false_type {};
 template <int R, int C, int O, int MR, int MC>
 struct is_data_matrix<Eigen::Matrix<double, R, C, O, MR, MC>> : std::true_type {};
 
+/**
+ * Zero-copy view of column-major double data that already lives somewhere else, e.g. the x_r
+ * array a map_rect functor receives:  data_matrix_view x(x_r.data(), rows, cols);
+ * The reference's GLMs only accept an owning Eigen::Matrix (value_of_rec has no Map overload,
+ * stan/math/prim/mat/fun/value_of_rec.hpp:22-49), so a functor has to copy x_r into a matrix on
+ * every call; the device path never reads x on the host after the first call, so it also takes a
+ * view (an extension: calls with a view exist only under STAN_CUDA).
+ */
+typedef Eigen::Map<const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>> data_matrix_view;
+template <>
+struct is_data_matrix<data_matrix_view> : std::true_type {};
+
 /** scalar, std::vector or Eigen vector whose scalar type satisfies Pred */
 template <typename T, template <typename> class Pred>
 struct is_scalar_or_vector_of : Pred<T> {};
@@ -197,6 +209,12 @@ inline void matrix_layout(const Eigen::Matrix<double, R, C, O, MR, MC>& x, const
   if (*ld < 1) {
     *ld = 1;
   }
+}
+
+inline void matrix_layout(const data_matrix_view& x, const double** data, int64_t* ld, int32_t* row_major) {
+  *data = x.data();
+  *row_major = 0;
+  *ld = x.rows() < 1 ? 1 : x.rows();
 }
 
 }  // namespace cuda

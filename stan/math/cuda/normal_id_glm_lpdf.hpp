@@ -19,7 +19,7 @@ namespace cuda {
  * alpha, beta, sigma go straight into edges 1, 3, 4, 5; lazy checks as :150-156.
  */
 template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta, typename T_scale>
-return_type_t<T_y, T_x, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y& y, const T_x& x,
+return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y& y, const T_x& x,
                                                                             const T_alpha& alpha,
                                                                             const T_beta& beta,
                                                                             const T_scale& sigma) {
@@ -39,14 +39,16 @@ return_type_t<T_y, T_x, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(cons
   if (size_zero(y, sigma)) {
     return 0;
   }
-  if (!include_summand<propto, T_y, T_x, T_alpha, T_beta, T_scale>::value) {
+  if (!include_summand<propto, T_y, double, T_alpha, T_beta, T_scale>::value) {
     return 0;
   }
 
   real_outcome<T_y> y_val(y, N);
   values<T_scale> sigma_val(sigma);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_NORMAL_ID, x, alpha, beta);
-  operands_and_partials<T_y, T_x, T_alpha, T_beta, T_scale> ops_partials(y, x, alpha, beta, sigma);
+  // x is data on this path: its (empty) edge is declared on a double so that views of x work too
+  const double x_placeholder = 0;
+  operands_and_partials<T_y, double, T_alpha, T_beta, T_scale> ops_partials(y, x_placeholder, alpha, beta, sigma);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_is_double = 1;

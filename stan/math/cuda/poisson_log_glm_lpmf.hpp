@@ -20,10 +20,10 @@ namespace cuda {
  * is true, so the propto variant returns 0 with a non-zero gradient.
  */
 template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta>
-return_type_t<T_x, T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T_x& x, const T_alpha& alpha,
+return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T_x& x, const T_alpha& alpha,
                                                                 const T_beta& beta) {
   static const char* function = "poisson_log_glm_lpmf";
-  using T_partials_return = partials_return_t<T_y, T_x, T_alpha, T_beta>;
+  using T_partials_return = partials_return_t<T_y, double, T_alpha, T_beta>;
   const size_t N = x.rows();
   const size_t M = x.cols();
 
@@ -37,14 +37,16 @@ return_type_t<T_x, T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, co
   if (size_zero(y)) {
     return 0;
   }
-  if (!include_summand<propto, T_x, T_alpha, T_beta>::value) {
+  if (!include_summand<propto, double, T_alpha, T_beta>::value) {
     check_nonnegative(function, "Vector of dependent variables", y);  // nothing goes to the device
     return 0;
   }
 
   int_outcome<T_y> y_val(y, N);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_POISSON_LOG, x, alpha, beta);
-  operands_and_partials<T_x, T_alpha, T_beta> ops_partials(x, alpha, beta);
+  // x is data on this path: its (empty) edge is declared on a double so that views of x work too
+  const double x_placeholder = 0;
+  operands_and_partials<double, T_alpha, T_beta> ops_partials(x_placeholder, alpha, beta);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_is_double = 0;

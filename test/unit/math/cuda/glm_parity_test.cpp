@@ -166,6 +166,24 @@ TEST(CudaGlmVariants, vector_alpha_vector_sigma_var_y) {
   stan::math::recover_memory();
 }
 
+TEST(CudaGlmVariants, zero_copy_data_view) {
+  Problem p = make_problem(4001, 37, 9);
+  vector_v beta = to_v(p.beta);
+  var alpha = 0.3, sigma = 1.3;
+  stan::math::cuda::data_matrix_view xv(p.x.data(), p.x.rows(), p.x.cols());
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("bernoulli view", bernoulli_logit_glm_lpmf(p.y_bern, xv, alpha, beta),
+                   bernoulli_logit_glm_lpmf_reference_cpu(p.y_bern, p.x, alpha, beta), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()));
+  STAN_CUDA_PARITY("poisson view propto", poisson_log_glm_lpmf<true>(p.y_pois, xv, alpha, beta),
+                   poisson_log_glm_lpmf_reference_cpu<true>(p.y_pois, p.x, alpha, beta), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()));
+  STAN_CUDA_PARITY("normal view", normal_id_glm_lpdf(p.y_norm, xv, alpha, beta, sigma),
+                   normal_id_glm_lpdf_reference_cpu(p.y_norm, p.x, alpha, beta, sigma), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, sigma.adj()));
+  stan::math::recover_memory();
+}
+
 TEST(CudaGlmVariants, zero_instances) {
   MatrixXd x(0, 2);
   std::vector<int> y;

@@ -1,11 +1,15 @@
 """Multi-GPU tests (need >= 2 B200s: `gpurun --gpus 2`): rows sharded over the devices of one
-process with an NCCL all-reduce of the result block, and shard scopes landing on distinct devices."""
-import numpy as np
+process with an all-reduce of the result block, and shard scopes landing on distinct devices.
+Each case runs tests/multi_gpu_worker.py in a fresh process (the device set is bound once per
+process)."""
+import os
+import subprocess
+import sys
+
 import pytest
 
-from tests.helpers import check_glm_result, synth_glm
-
 pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _n_gpus():
@@ -13,47 +17,32 @@ def _n_gpus():
     return torch.cuda.device_count()
 
 
-@pytest.fixture(scope="module")
-def glm2():
+def _run(*args):
     if _n_gpus() < 2:
         pytest.skip("needs 2 GPUs")
-    from math_b200 import glm
-    from math_b200._lib import lib
-    glm.init(0)
-    if lib().stan_cuda_device_count() < 2:
-        pytest.skip("library was initialised with one device earlier in this process")
-    return glm
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "multi_gpu_worker.py"), *args],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "OK" in r.stdout, r.stdout[-3000:]
 
 
 @pytest.mark.parametrize("family", ["poisson_log", "normal_id"])
-def test_in_process_row_sharding_with_nccl(glm2, family):
-    from math_b200._lib import lib
-    from oracle import loader as L
-    lib().stan_cuda_set_shard_min_elems(1 << 16)
-    n, k = 200_003, 48
-    s = synth_glm(family, n, k, seed=17)
-    ref = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"])
-    st0 = glm2.stats()
-    got = glm2.glm_eval(family, s["y"], s["x"], s["alpha"], s["beta"], s["sigma"])
-    st1 = glm2.stats()
-    check_glm_result(got, ref, "sharded " + family)
-    assert st1["allreduces"] - st0["allreduces"] == 1
-    assert st1["kernel_launches"] - st0["kernel_launches"] >= 2
-    # vector alpha: per-row partials come back from each device's row block
-    alpha = 0.3 + 0.05 * np.random.default_rng(1).standard_normal(n)
-    ref = L.oracle_glm(family, s["x"], s["y"], alpha, s["beta"], s["sigma"])
-    got = glm2.glm_eval(family, s["y"], s["x"], alpha, s["beta"], s["sigma"])
-    check_glm_result(got, ref, "sharded vector alpha " + family)
-    glm2.cache_clear()
-    lib().stan_cuda_set_shard_min_elems(1 << 24)
+def test_in_process_row_sharding(family):
+    _run("sharding", family)
 
 
-def test_shard_scopes_use_distinct_devices(glm2):
-    from oracle import loader as L
-    s = synth_glm("bernoulli_logit", 30000, 32, seed=4)
-    ref = L.oracle_glm("bernoulli_logit", s["x"], s["y"], s["alpha"], s["beta"])
-    for job in range(4):
-        with glm2.shard_scope(call_id=9, job=job, device=job % 2):
-            got = glm2.glm_eval("bernoulli_logit", s["y"], s["x"], s["alpha"], s["beta"])
-        check_glm_result(got, ref, "scope job %d" % job)
-    glm2.cache_clear()
+def test_shard_scopes_use_distinct_devices():
+    _run("scopes")
+
+
+def test_torchrun_two_ranks_bench_line():
+    """bench.py under torchrun with 2 ranks: one JSON line, device and host-level paths agree."""
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    import json
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "bench.py"),
+                        "--gpus", "2", "--steps", "5", "--warmup", "3", "--n", "400000", "--k", "64",
+                        "--no-cpu-baseline"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert line["n_gpus"] == 2 and line["consistent_device_vs_host_api"] and line["value"] > 0
