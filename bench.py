@@ -215,9 +215,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--n", type=int, default=0, help="override rows (sweeps only)")
-    ap.add_argument("--k", type=int, default=0, help="override columns (sweeps only)")
+    ap.add_argument("--n", "--rows", dest="n", type=int, default=0, help="override rows (sweeps only)")
+    ap.add_argument("--k", "--cols", dest="k", type=int, default=0, help="override columns (sweeps only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--collective", default="auto", choices=["auto", "fused", "nccl"],
+                    help="N>1: all-reduce inside the fused kernel over peer memory, or ncclAllReduce behind it")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -233,6 +235,8 @@ def main():
         run_reference(args, family, n, k, desc)
         return
 
+    if args.collective == "nccl":
+        os.environ["STAN_CUDA_FUSED_ALLREDUCE"] = "0"
     import torch
     import torch.distributed as dist
     from math_b200 import _abi, glm
@@ -256,6 +260,10 @@ def main():
     x, y, alpha, beta, sigma = synth_shard(family, rows, k, seed=1000 + rank)
     fam = FAM_ID[family]
     flags = glm.glm_flags(fam, False)
+    fused = world > 1 and bool(lib().stan_cuda_comm_fused_available())
+    if args.collective == "fused" and world > 1 and not fused:
+        raise SystemExit("bench.py: --collective fused but no peer exchange: " + lib().stan_cuda_comm_describe().decode())
+    launch_flags = flags | (_abi.FUSED_ALLREDUCE if fused else 0)
 
     def barrier():
         torch.cuda.synchronize()
@@ -276,8 +284,8 @@ def main():
     sptr = stream.cuda_stream
 
     def device_step():
-        data.launch(flags, d_params.data_ptr(), d_result.data_ptr(), sptr)
-        if world > 1:
+        data.launch(launch_flags, d_params.data_ptr(), d_result.data_ptr(), sptr)
+        if world > 1 and not fused:
             check(lib().stan_cuda_allreduce(d_result.data_ptr(), data.result_len, sptr))
 
     with torch.cuda.stream(stream):
@@ -295,9 +303,9 @@ def main():
         ev0.record(stream)
         for i in range(args.steps):
             kev[i][0].record(stream)
-            data.launch(flags, d_params.data_ptr(), d_result.data_ptr(), sptr)
+            data.launch(launch_flags, d_params.data_ptr(), d_result.data_ptr(), sptr)
             kev[i][1].record(stream)
-            if world > 1:
+            if world > 1 and not fused:
                 check(lib().stan_cuda_allreduce(d_result.data_ptr(), data.result_len, sptr))
         ev1.record(stream)
     barrier()
@@ -341,7 +349,8 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": desc, "family": family, "n": n, "k": k, "rows_per_gpu": rows,
-                       "parallelism": "rows/%d + ncclAllReduce(%d f64)" % (world, data.result_len) if world > 1 else "1 GPU",
+                       "parallelism": ("rows/%d + %s(%d f64)" % (world, "all-reduce fused into glm_fused_kernel over NVLink peer memory"
+                                                                 if fused else "ncclAllReduce", data.result_len)) if world > 1 else "1 GPU",
                        "l2": "no flush: per-GPU input %.2f GB is larger than the 126 MB L2" % (alg_bytes / 1e9)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(args.workload), "peak_source": peak_src,

@@ -83,6 +83,10 @@ extern "C" {
 #define STAN_CUDA_NEED_DSIGMA 0x20u
 #define STAN_CUDA_NEED_DY 0x40u
 #define STAN_CUDA_NEED_ALL 0x78u
+/* stan_cuda_glm_launch only: sum the result block over the ranks of the communicator INSIDE the
+ * fused kernel (peer exchange over NVLink, see stan_cuda_comm_fused_available) instead of a
+ * separate stan_cuda_allreduce.  Every rank must launch with the flag, in the same order. */
+#define STAN_CUDA_FUSED_ALLREDUCE 0x100u
 
 typedef struct stan_cuda_glm_args {
   int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID */
@@ -132,6 +136,7 @@ typedef struct stan_cuda_stats_t {
   uint64_t kernel_launches;  /* launches of this library's own kernels */
   uint64_t allreduces;       /* NCCL all-reduce calls */
   double last_fill_ms;       /* wall time of the most recent cache fill */
+  uint64_t fused_allreduces; /* all-reduces done inside the fused kernel over peer memory */
 } stan_cuda_stats_t;
 
 /* ---- context -------------------------------------------------------------------------- */
@@ -175,10 +180,18 @@ STAN_CUDA_API void stan_cuda_shard_scope_exit(void);
 /* ---- multi-process communicator (one process per GPU) --------------------------------------- */
 /* Rank 0 creates the id; the host plumbing (torch.distributed, MPI, a file) carries the 128 bytes
  * to every rank; every rank then calls comm_init_rank.  After that, sharded evaluations
- * all-reduce [lp-parts, dbeta] across ranks with ncclAllReduce on the evaluation stream. */
+ * all-reduce [lp-parts, dbeta] across ranks: inside the fused kernel over peer memory when
+ * available (below), else with ncclAllReduce on the evaluation stream. */
 STAN_CUDA_API int stan_cuda_comm_unique_id(void* id128);
 STAN_CUDA_API int stan_cuda_comm_init_rank(int world_size, int rank, const void* id128);
 STAN_CUDA_API int stan_cuda_comm_world_size(void);
+/* 1 when comm_init_rank could map every rank's exchange block into every other rank (CUDA IPC over
+ * NVLink/NVSwitch peer access): the all-reduce then runs inside the fused kernel -- the last CTA pushes
+ * its K+4 doubles into every peer's block, waits for the peers' flags and adds the blocks in rank
+ * order -- and no ncclAllReduce is launched.  0: ncclAllReduce behind the kernel (same results up to
+ * summation order).  Environment STAN_CUDA_FUSED_ALLREDUCE=0 forces 0. */
+STAN_CUDA_API int stan_cuda_comm_fused_available(void);
+STAN_CUDA_API const char* stan_cuda_comm_describe(void);
 STAN_CUDA_API void stan_cuda_comm_destroy(void);
 
 /* ---- device-level API (streams and buffers owned by the caller, e.g. torch) ---------------- */

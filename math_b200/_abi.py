@@ -14,6 +14,7 @@ FAMILIES = {"bernoulli_logit": BERNOULLI_LOGIT, "poisson_log": POISSON_LOG, "nor
 
 LP_CONST, LP_SCALE, LP_MAIN, LP_ALL = 0x01, 0x02, 0x04, 0x07
 NEED_DBETA, NEED_DALPHA, NEED_DSIGMA, NEED_DY, NEED_ALL = 0x08, 0x10, 0x20, 0x40, 0x78
+FUSED_ALLREDUCE = 0x100
 
 c_double_p = C.POINTER(C.c_double)
 
@@ -70,6 +71,7 @@ class Stats(C.Structure):
         ("kernel_launches", C.c_uint64),
         ("allreduces", C.c_uint64),
         ("last_fill_ms", C.c_double),
+        ("fused_allreduces", C.c_uint64),
     ]
 
 
@@ -94,6 +96,8 @@ PROTOTYPES = {
     "stan_cuda_comm_unique_id": (C.c_int, [C.c_void_p]),
     "stan_cuda_comm_init_rank": (C.c_int, [C.c_int, C.c_int, C.c_void_p]),
     "stan_cuda_comm_world_size": (C.c_int, []),
+    "stan_cuda_comm_fused_available": (C.c_int, []),
+    "stan_cuda_comm_describe": (C.c_char_p, []),
     "stan_cuda_comm_destroy": (None, []),
     "stan_cuda_data_create": (C.c_int, [C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64,
                                         C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),

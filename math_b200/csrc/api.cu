@@ -210,6 +210,23 @@ int glm_eval(const stan_cuda_glm_args* a) {
   const int world = comm_world_size();
   if (world > 1 && S > 1) return fail(STAN_CUDA_ERR_STATE, "multi-process communicator with several devices per process");
 
+  // Sharded evaluations of one process are serialised: the devices then see the collectives of
+  // different host threads in the same order (required by the in-kernel exchange and by NCCL).
+  static std::mutex sharded_mu;
+  std::unique_lock<std::mutex> sharded_lock(sharded_mu, std::defer_lock);
+  PeerXchg* xchg = nullptr;   // [S] views (in-process) or this rank's view (multi-process)
+  unsigned long long xchg_seq = 0;
+  if (S > 1) {
+    sharded_lock.lock();
+    std::vector<int> devs(S);
+    for (size_t s = 0; s < S; ++s) devs[s] = e->shards[s].d->device;
+    xchg = comm_local_xchg(devs);
+    if (xchg) xchg_seq = ++xchg[0].seq;
+  } else if (world > 1) {
+    xchg = comm_rank_xchg();
+    if (xchg) xchg_seq = ++xchg->seq;
+  }
+
   std::vector<ShardRun> runs(S);
   const int kpad = e->shards[0].d->t.kpad;
   const size_t np = size_t(kpad) + 2, nr = size_t(kpad) + 4;
@@ -245,10 +262,16 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (sigma_vec)
       SC_CUDA(cudaMemcpyAsync(run.d_sigma, a->sigma + r0, size_t(rows) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     LaunchIO io{a->flags, run.d_params, run.d_alpha, run.d_sigma, run.d_result, run.d_rowa, run.d_rows};
+    if (xchg) {
+      io.xchg = S > 1 ? &xchg[s] : xchg;
+      io.xchg_seq = xchg_seq;
+    }
     SC_TRY(launch_glm(d, io, &td->ws, td->stream));
   }
-  // combine the additive result blocks of the row shards
-  if (S > 1) {
+  // combine the additive result blocks of the row shards (unless the kernel already did)
+  if (xchg) {
+    counters().fused_allreduces.fetch_add(1, std::memory_order_relaxed);
+  } else if (S > 1) {
     std::vector<int> devs(S);
     std::vector<double*> bufs(S);
     std::vector<cudaStream_t> streams(S);

@@ -13,6 +13,8 @@
 // dependency (torch's bundled NCCL is reused when the process already has it).
 #include <dlfcn.h>
 
+#include <cstring>
+
 #include "context.cuh"
 
 namespace stancuda {
@@ -30,6 +32,7 @@ struct NcclApi {
   int (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
   int (*CommDestroy)(ncclComm_t) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
   int (*GroupStart)() = nullptr;
   int (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
@@ -42,6 +45,12 @@ static ncclComm_t g_rank_comm = nullptr;
 static int g_world = 1, g_rank = 0, g_rank_device = -1;
 static std::vector<ncclComm_t> g_local_comms;
 static std::vector<int> g_local_devices;
+// peer exchange state (fused all-reduce)
+static PeerXchg g_rank_xchg;                    // multi-process: this rank's view
+static std::vector<void*> g_rank_ipc_opened;    // peer blocks opened with cudaIpcOpenMemHandle
+static std::vector<PeerXchg> g_local_xchg;      // in-process: one view per device
+static std::vector<int> g_local_xchg_devices;
+static std::string g_xchg_note = "not initialised";
 
 static int fail_nccl(int rc, const char* what) {
   std::string s = std::string("NCCL error in ") + what + ": ";
@@ -67,6 +76,7 @@ static int load_nccl_locked() {
   SC_SYM(CommInitAll, "ncclCommInitAll")
   SC_SYM(CommDestroy, "ncclCommDestroy")
   SC_SYM(AllReduce, "ncclAllReduce")
+  SC_SYM(AllGather, "ncclAllGather")
   SC_SYM(GroupStart, "ncclGroupStart")
   SC_SYM(GroupEnd, "ncclGroupEnd")
   SC_SYM(GetErrorString, "ncclGetErrorString")
@@ -74,6 +84,127 @@ static int load_nccl_locked() {
 #undef SC_SYM
   g_api.handle = h;
   return STAN_CUDA_OK;
+}
+
+bool fused_allreduce_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("STAN_CUDA_FUSED_ALLREDUCE");
+    return !(v && *v == '0');
+  }();
+  return on;
+}
+
+// ---- peer exchange set-up ----------------------------------------------------------------------
+// Multi-process: every rank allocates its block, the CUDA IPC handles travel through one
+// ncclAllGather, every rank maps the others' blocks; a final ncclAllReduce of an ok-flag makes the
+// decision unanimous (and doubles as the barrier after which peers may write).
+static int setup_rank_xchg_locked(int world, int rank, int dev) {
+  g_rank_xchg = PeerXchg();
+  if (!fused_allreduce_enabled()) { g_xchg_note = "disabled by STAN_CUDA_FUSED_ALLREDUCE=0"; return STAN_CUDA_OK; }
+  if (world > kXchgMaxWorld) { g_xchg_note = "world larger than 16"; return STAN_CUDA_OK; }
+  SC_CUDA(cudaSetDevice(dev));
+  double ok = 1.0;
+  double* local = nullptr;
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (cudaMalloc(reinterpret_cast<void**>(&local), xchg_block_bytes(world)) != cudaSuccess ||
+      cudaMemset(local, 0, xchg_block_bytes(world)) != cudaSuccess ||
+      cudaIpcGetMemHandle(&mine, local) != cudaSuccess) {
+    cudaGetLastError();
+    ok = 0.0;
+  }
+  // gather the handles
+  const size_t hb = sizeof(cudaIpcMemHandle_t);
+  unsigned char* d_handles = nullptr;
+  double* d_ok = nullptr;
+  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_handles), hb * (world + 1)));
+  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_ok), sizeof(double)));
+  SC_CUDA(cudaMemcpy(d_handles + hb * world, &mine, hb, cudaMemcpyHostToDevice));
+  int rc = g_api.AllGather(d_handles + hb * world, d_handles, hb, /*ncclChar*/ 0, g_rank_comm, nullptr);
+  if (rc != ncclSuccess) return fail_nccl(rc, "ncclAllGather (ipc handles)");
+  SC_CUDA(cudaStreamSynchronize(nullptr));
+  std::vector<cudaIpcMemHandle_t> all(world);
+  SC_CUDA(cudaMemcpy(all.data(), d_handles, hb * world, cudaMemcpyDeviceToHost));
+  PeerXchg x;
+  x.world = world;
+  x.rank = rank;
+  x.local = local;
+  std::vector<void*> opened;
+  for (int q = 0; q < world && ok > 0; ++q) {
+    if (q == rank) { x.peers[q] = local; continue; }
+    void* ptr = nullptr;
+    if (cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      ok = 0.0;
+      break;
+    }
+    opened.push_back(ptr);
+    x.peers[q] = static_cast<double*>(ptr);
+  }
+  SC_CUDA(cudaMemcpy(d_ok, &ok, sizeof(double), cudaMemcpyHostToDevice));
+  rc = g_api.AllReduce(d_ok, d_ok, 1, ncclFloat64, ncclSum, g_rank_comm, nullptr);
+  if (rc != ncclSuccess) return fail_nccl(rc, "ncclAllReduce (peer exchange agreement)");
+  SC_CUDA(cudaStreamSynchronize(nullptr));
+  double total = 0.0;
+  SC_CUDA(cudaMemcpy(&total, d_ok, sizeof(double), cudaMemcpyDeviceToHost));
+  cudaFree(d_handles);
+  cudaFree(d_ok);
+  if (total == double(world)) {
+    g_rank_xchg = x;
+    g_rank_ipc_opened = opened;
+    g_xchg_note = "fused peer exchange over CUDA IPC";
+  } else {
+    for (void* ptr : opened) cudaIpcCloseMemHandle(ptr);
+    if (local) cudaFree(local);
+    g_xchg_note = "CUDA IPC peer mapping unavailable on some rank: ncclAllReduce is used";
+  }
+  return STAN_CUDA_OK;
+}
+
+PeerXchg* comm_rank_xchg() { return g_rank_xchg.world > 1 ? &g_rank_xchg : nullptr; }
+
+// In-process: peer access between every pair of devices, one block per device.
+PeerXchg* comm_local_xchg(const std::vector<int>& devices) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!fused_allreduce_enabled()) return nullptr;
+  const int world = int(devices.size());
+  if (world < 2 || world > kXchgMaxWorld) return nullptr;
+  if (g_local_xchg_devices == devices) return g_local_xchg.empty() ? nullptr : g_local_xchg.data();
+  g_local_xchg_devices = devices;
+  g_local_xchg.clear();
+  std::vector<double*> blocks(world, nullptr);
+  bool ok = true;
+  for (int i = 0; i < world && ok; ++i) {
+    ok = cudaSetDevice(devices[i]) == cudaSuccess;
+    for (int j = 0; j < world && ok; ++j) {
+      if (i == j) continue;
+      int can = 0;
+      ok = cudaDeviceCanAccessPeer(&can, devices[i], devices[j]) == cudaSuccess && can;
+      if (ok) {
+        cudaError_t e = cudaDeviceEnablePeerAccess(devices[j], 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+        ok = e == cudaSuccess;
+      }
+    }
+    if (ok) ok = cudaMalloc(reinterpret_cast<void**>(&blocks[i]), xchg_block_bytes(world)) == cudaSuccess &&
+                 cudaMemset(blocks[i], 0, xchg_block_bytes(world)) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess;
+  }
+  if (!ok) {
+    cudaGetLastError();
+    for (int i = 0; i < world; ++i)
+      if (blocks[i]) { cudaSetDevice(devices[i]); cudaFree(blocks[i]); }
+    g_xchg_note = "peer access between the devices of the process unavailable: ncclAllReduce is used";
+    return nullptr;
+  }
+  g_local_xchg.resize(world);
+  for (int i = 0; i < world; ++i) {
+    g_local_xchg[i].world = world;
+    g_local_xchg[i].rank = i;
+    g_local_xchg[i].local = blocks[i];
+    for (int q = 0; q < world; ++q) g_local_xchg[i].peers[q] = blocks[q];
+  }
+  g_xchg_note = "fused peer exchange (in-process peer access)";
+  return g_local_xchg.data();
 }
 
 int comm_world_size() { return g_world; }
@@ -154,13 +285,25 @@ int stan_cuda_comm_init_rank(int world_size, int rank, const void* id128) {
   g_world = world_size;
   g_rank = rank;
   g_rank_device = dev;
+  if (world_size > 1) SC_TRY(setup_rank_xchg_locked(world_size, rank, dev));
   return STAN_CUDA_OK;
 }
 
 int stan_cuda_comm_world_size(void) { return g_world; }
 
+int stan_cuda_comm_fused_available(void) { return g_rank_xchg.world > 1 ? 1 : 0; }
+
+const char* stan_cuda_comm_describe(void) { return g_xchg_note.c_str(); }
+
 void stan_cuda_comm_destroy(void) {
   std::lock_guard<std::mutex> lk(g_mu);
+  if (g_rank_xchg.world > 1) {
+    cudaDeviceSynchronize();
+    for (void* ptr : g_rank_ipc_opened) cudaIpcCloseMemHandle(ptr);
+    g_rank_ipc_opened.clear();
+    if (g_rank_xchg.local) cudaFree(g_rank_xchg.local);
+    g_rank_xchg = PeerXchg();
+  }
   if (g_rank_comm && g_api.CommDestroy) g_api.CommDestroy(g_rank_comm);
   g_rank_comm = nullptr;
   g_world = 1;

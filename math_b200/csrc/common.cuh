@@ -78,6 +78,8 @@ struct stan_cuda_data {
 
 namespace stancuda {
 
+struct PeerXchg;
+
 struct LaunchIO {
   uint32_t flags;
   const double* d_params;     // [kpad] beta, [kpad] alpha, [kpad+1] sigma
@@ -86,6 +88,8 @@ struct LaunchIO {
   double* d_result;           // [kpad + 4]
   double* d_row_dalpha;       // n or null
   double* d_row_dsigma;       // n or null
+  const struct PeerXchg* xchg = nullptr;  // non-null: all-reduce fused into the kernel (comm.cu)
+  unsigned long long xchg_seq = 0;
 };
 
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.
@@ -116,7 +120,7 @@ int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream
 // counters
 struct Counters {
   std::atomic<uint64_t> cache_hits{0}, cache_misses{0}, bytes_uploaded{0}, evals{0}, launches{0},
-      allreduces{0};
+      allreduces{0}, fused_allreduces{0};
   std::atomic<double> last_fill_ms{0};
 };
 Counters& counters();

@@ -219,6 +219,7 @@ int stan_cuda_stats(stan_cuda_stats_t* out) {
   out->kernel_launches = c.launches.load();
   out->allreduces = c.allreduces.load();
   out->last_fill_ms = c.last_fill_ms.load();
+  out->fused_allreduces = c.fused_allreduces.load();
   return STAN_CUDA_OK;
 }
 
@@ -230,6 +231,7 @@ void stan_cuda_stats_reset(void) {
   c.evals = 0;
   c.launches = 0;
   c.allreduces = 0;
+  c.fused_allreduces = 0;
   c.last_fill_ms = 0.0;
 }
 

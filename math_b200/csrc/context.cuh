@@ -35,6 +35,27 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
                     stan_cuda_data** out);
 void free_data_block(stan_cuda_data* d);
 
+// Peer exchange (comm.cu): all-reduce fused into the GLM kernel over NVLink peer memory --------
+// Every device owns one exchange block; the last CTA of the fused kernel pushes its result block
+// into slot [seq & 1][rank] of EVERY device's block (plain stores to peer-mapped memory), raises
+// a flag per peer, waits for the world's flags in its own block and adds the blocks in rank order.
+constexpr int kXchgMaxWorld = 16;
+constexpr int kXchgCols = 520;  // >= kpad_max (512) + 4, per-rank stride in doubles
+struct PeerXchg {
+  int world = 0;                       // 0: not available
+  int rank = 0;
+  double* local = nullptr;             // this device's block: [2][world][kXchgCols] doubles + flags
+  double* peers[kXchgMaxWorld] = {};   // peers[q]: device q's block as mapped into this device
+  unsigned long long seq = 0;          // sequence number of the collective (same on every rank)
+};
+inline size_t xchg_flag_offset_doubles(int world) { return size_t(2) * world * kXchgCols; }
+inline size_t xchg_block_bytes(int world) { return (xchg_flag_offset_doubles(world) + size_t(2) * world + 8) * sizeof(double); }
+// multi-process communicator: exchange of this rank, or world == 0 (fall back to ncclAllReduce)
+PeerXchg* comm_rank_xchg();
+// in-process communicator over `devices`: exchanges per device (index = position), or nullptr
+PeerXchg* comm_local_xchg(const std::vector<int>& devices);
+bool fused_allreduce_enabled();
+
 // NCCL (comm.cu) -------------------------------------------------------------------------------
 int comm_world_size();                       // ranks of the multi-process communicator (1 if none)
 int comm_allreduce_rank(double* d_buf, int64_t count, cudaStream_t stream);

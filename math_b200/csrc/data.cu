@@ -298,6 +298,14 @@ int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_par
   if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: null argument");
   SC_CUDA(cudaSetDevice(d->device));
   LaunchIO io{flags, d_params, d_alpha_vec, d_sigma_vec, d_result, d_row_dalpha, d_row_dsigma};
+  if (flags & STAN_CUDA_FUSED_ALLREDUCE) {
+    PeerXchg* x = comm_rank_xchg();
+    if (!x) return fail(STAN_CUDA_ERR_STATE, "stan_cuda_glm_launch: STAN_CUDA_FUSED_ALLREDUCE without a peer exchange "
+                                             "(stan_cuda_comm_fused_available() is 0)");
+    io.xchg = x;
+    io.xchg_seq = ++x->seq;
+    counters().fused_allreduces.fetch_add(1, std::memory_order_relaxed);
+  }
   return launch_glm(d, io, &d->ws, static_cast<cudaStream_t>(stream));
 }
 

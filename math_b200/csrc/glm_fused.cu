@@ -24,7 +24,7 @@
 //    CTA to finish (atomic ticket) adds the CTA partials in CTA order -> bit-reproducible.
 #include <math.h>
 
-#include "common.cuh"
+#include "context.cuh"
 
 namespace stancuda {
 
@@ -50,6 +50,11 @@ struct GlmKernelParams {
   double* result;
   uint32_t flags;
   double lgamma_sum;
+  // all-reduce fused into the kernel (peer exchange over NVLink, comm.cu); world <= 1: off
+  int xchg_world, xchg_rank;
+  unsigned long long xchg_seq;
+  double* xchg_local;
+  double* xchg_peers[kXchgMaxWorld];
 #ifdef STAN_CUDA_PHASE_TIMERS
   unsigned long long* timers;  // [grid][4] globaltimer stamps: start, first tile landed, loop end, CTA partial written; [grid*4] = end of last CTA
 #endif
@@ -110,6 +115,75 @@ __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint
       "[%0], [%1], %2, [%3], %4;" ::"r"(dst),
       "l"(src), "r"(bytes), "r"(bar), "l"(policy)
       : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// All-reduce of the result block fused into the kernel (replaces kernel -> ncclAllReduce).
+// Runs in the last CTA only.  fin[0..cols) holds this device's block on entry and the sum over
+// the world, added in rank order (bit-identical on every rank), on exit.
+//   push : fin -> slot [seq & 1][rank] of EVERY device's exchange block (stores to peer-mapped
+//          memory travel over NVLink), __threadfence_system, then one release-store of `seq` into
+//          that device's flag [seq & 1][rank];
+//   wait : acquire-loads of the world's flags in the own block until they show `seq`;
+//   sum  : system-scope loads of the world's slots in rank order.
+// Two slots suffice: a rank can be at most one collective ahead of the slowest rank, because it
+// cannot finish collective s before every rank has pushed its block of collective s.
+// A rank that does not show up within 30 s makes the result NaN (no hang).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(unsigned long long* ptr, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* ptr) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(ptr) : "memory");
+  return v;
+}
+__device__ __forceinline__ double ld_relaxed_sys(const double* ptr) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(ptr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+template <int THREADS>
+__device__ __forceinline__ void xchg_allreduce(const GlmKernelParams& p, double* fin, int cols, int tid,
+                                               int* s_flag) {
+  const int world = p.xchg_world, rank = p.xchg_rank;
+  const unsigned long long seq = p.xchg_seq;
+  const size_t slot = size_t(seq & 1ull) * world;
+  const size_t flag0 = size_t(2) * world * kXchgCols;  // flags follow the slots (as 8-byte words)
+  for (int idx = tid; idx < world * cols; idx += THREADS) {
+    const int q = idx / cols, c = idx - q * cols;
+    p.xchg_peers[q][(slot + rank) * kXchgCols + c] = fin[c];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < world)
+    st_release_sys(reinterpret_cast<unsigned long long*>(p.xchg_peers[tid] + flag0) + slot + rank, seq);
+  if (tid == 0) *s_flag = 0;
+  __syncthreads();
+  if (tid < world) {
+    const unsigned long long* f = reinterpret_cast<const unsigned long long*>(p.xchg_local + flag0) + slot + tid;
+    const unsigned long long t0 = global_timer_ns();
+    while (ld_acquire_sys(f) != seq) {
+      if (global_timer_ns() - t0 > 30000000000ull) {
+        atomicExch(s_flag, 1);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  const bool timed_out = *s_flag != 0;
+  for (int c = tid; c < cols; c += THREADS) {
+    double sum = 0.0;
+    for (int q = 0; q < world; ++q) sum += ld_relaxed_sys(p.xchg_local + (slot + q) * kXchgCols + c);
+    fin[c] = timed_out ? __longlong_as_double(0x7ff8dead00000000ll) : sum;
+  }
+  __syncthreads();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -370,6 +444,7 @@ glm_fused_kernel(const GlmKernelParams p) {
   __syncthreads();
   if (!s_is_last) return;
   __threadfence();
+  double* fin = reinterpret_cast<double*>(stage0);  // [cols]; every stage has been consumed by now
   for (int c = tid; c < cols; c += THREADS) {
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
     int b = 0;
@@ -381,7 +456,7 @@ glm_fused_kernel(const GlmKernelParams p) {
     }
     for (; b < ngroups; ++b) s0 += __ldcg(gscratch + size_t(b) * cols + c);
     const double tot = (s0 + s1) + (s2 + s3);
-    if (c >= 4) p.result[c] = tot;
+    if (c >= 4) fin[c] = tot;
     else part[c] = tot;
   }
   __syncthreads();
@@ -405,15 +480,20 @@ glm_fused_kernel(const GlmKernelParams p) {
       if (!p.sigma_vec) dsig = (A2 - nn) * inv_sigma0;  // :142-143
       witness = A2;  // :150 tests y_scaled_sq_sum
     }
-    p.result[0] = lp;
-    p.result[1] = A1;
-    p.result[2] = dsig;
-    p.result[3] = witness;
+    fin[0] = lp;
+    fin[1] = A1;
+    fin[2] = dsig;
+    fin[3] = witness;
     *p.ticket = 0u;  // ready for the next launch on this workspace (stream ordered)
-#ifdef STAN_CUDA_PHASE_TIMERS
-    if (p.timers) p.timers[size_t(grid) * 4] = gtimer();
-#endif
   }
+  __syncthreads();
+  // every term of the block is additive over row shards: sum it over the devices right here
+  if (p.xchg_world > 1) xchg_allreduce<THREADS>(p, fin, cols, tid, &s_is_last);
+  for (int c = tid; c < cols; c += THREADS) p.result[c] = fin[c];
+#ifdef STAN_CUDA_PHASE_TIMERS
+  __syncthreads();
+  if (tid == 0 && p.timers) p.timers[size_t(grid) * 4] = gtimer();
+#endif
 }
 
 }  // namespace stancuda
@@ -568,6 +648,18 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
   p.result = io.d_result;
   p.flags = io.flags;
   p.lgamma_sum = d->lgamma_sum;
+  p.xchg_world = 0;
+  p.xchg_rank = 0;
+  p.xchg_seq = io.xchg_seq;
+  p.xchg_local = nullptr;
+  for (int q = 0; q < kXchgMaxWorld; ++q) p.xchg_peers[q] = nullptr;
+  if (io.xchg && io.xchg->world > 1) {
+    if (t.kpad + 4 > kXchgCols) return fail(STAN_CUDA_ERR_ARG, "launch_glm: result block exceeds the exchange slot");
+    p.xchg_world = io.xchg->world;
+    p.xchg_rank = io.xchg->rank;
+    p.xchg_local = io.xchg->local;
+    for (int q = 0; q < io.xchg->world; ++q) p.xchg_peers[q] = io.xchg->peers[q];
+  }
 #ifdef STAN_CUDA_PHASE_TIMERS
   p.timers = g_phase_timers;
 #endif

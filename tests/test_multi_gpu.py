@@ -41,7 +41,7 @@ def test_torchrun_two_ranks_bench_line():
     import json
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                         "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "bench.py"),
-                        "--gpus", "2", "--steps", "5", "--warmup", "3", "--n", "400000", "--k", "64",
+                        "--gpus", "2", "--steps", "5", "--warmup", "3", "--rows", "400000", "--cols", "64",
                         "--no-cpu-baseline"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
     assert r.returncode == 0, r.stderr[-3000:]
     line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
