@@ -218,6 +218,7 @@ def main():
     ap.add_argument("--n", "--rows", dest="n", type=int, default=0, help="override rows (sweeps only)")
     ap.add_argument("--k", "--cols", dest="k", type=int, default=0, help="override columns (sweeps only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel", default="warp", choices=["warp", "cta"], help="kernel variant (glm_warp.cu | glm_fused.cu)")
     ap.add_argument("--collective", default="auto", choices=["auto", "fused", "nccl"],
                     help="N>1: all-reduce inside the fused kernel over peer memory, or ncclAllReduce behind it")
     args = ap.parse_args()
@@ -235,6 +236,8 @@ def main():
         run_reference(args, family, n, k, desc)
         return
 
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: one JSON line only
     if args.collective == "nccl":
         os.environ["STAN_CUDA_FUSED_ALLREDUCE"] = "0"
     import torch
@@ -251,6 +254,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     glm.init_device(local_rank)
+    lib().stan_cuda_set_kernel(1 if args.kernel == "warp" else 0)
     if world > 1:
         glm.comm_init_from_torch(dist)
 
@@ -355,7 +359,7 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kernel_ms,
-                         "kernel": "glm_fused_kernel"},
+                         "kernel": "glm_warp_kernel" if args.kernel == "warp" else "glm_fused_kernel"},
             "e2e": {"value": args.steps / (e2e_ms * 1e-3), "unit": "evals/s",
                     "h2d_bytes_per_step": int(data.params_len * 8), "d2h_bytes_per_step": int(data.result_len * 8),
                     "ms_per_step": e2e_ms / args.steps,

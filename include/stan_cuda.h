@@ -159,6 +159,10 @@ STAN_CUDA_API void stan_cuda_set_shard_min_elems(int64_t elems);
  * pipeline stages and resident CTAs per SM.  0 = automatic, negative = leave unchanged.
  * Environment: STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM. */
 STAN_CUDA_API void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm);
+/* Kernel variant for data created afterwards: 1 (default) = warp-synchronous kernel with a TMA
+ * producer warp (csrc/glm_warp.cu), 0 = CTA-synchronous kernel (csrc/glm_fused.cu).  Both compute
+ * the same thing from differently tiled copies of X.  Environment: STAN_CUDA_KERNEL=warp|cta. */
+STAN_CUDA_API void stan_cuda_set_kernel(int variant);
 
 /* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */
 STAN_CUDA_API int stan_cuda_glm_eval(const stan_cuda_glm_args* a);

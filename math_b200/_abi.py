@@ -86,6 +86,7 @@ PROTOTYPES = {
     "stan_cuda_stats_reset": (None, []),
     "stan_cuda_set_shard_min_elems": (None, [C.c_int64]),
     "stan_cuda_set_tuning": (None, [C.c_int, C.c_int, C.c_int]),
+    "stan_cuda_set_kernel": (None, [C.c_int]),
     "stan_cuda_glm_eval": (C.c_int, [C.POINTER(GlmArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
     "stan_cuda_cache_invalidate": (C.c_int, [C.c_void_p]),

@@ -37,7 +37,17 @@ int fail_cuda(cudaError_t e, const char* expr, const char* file, int line);
 // row r and the kc columns [cg*kc, (cg+1)*kc);  C * R == threads,  kpad == C * kc,  kc <= 16.
 constexpr int kMaxKc = 16;
 
+// Two tile layouts, one per kernel variant (STAN_CUDA_KERNEL=cta|warp, default warp):
+//   kLayoutCta  (glm_fused.cu) x_dev[(tile * kpad + col) * R + r]
+//   kLayoutWarp (glm_warp.cu)  8 consumer warps; the C column groups of a row sit in one warp:
+//               rows per warp rpw = 32 / C, R = 8 * rpw, element (r, col) of a tile with
+//               w = r / rpw, rl = r % rpw, cg = col / kc, j = col % kc lives at
+//               x_dev[tile * kpad * R + (j * 8 + w) * 32 + rl * C + cg]
+constexpr int kLayoutCta = 0;
+constexpr int kLayoutWarp = 1;
+
 struct Tiling {
+  int layout;   // kLayoutCta | kLayoutWarp
   int threads;  // consumer threads per CTA (128 | 256 | 512)
   int C;        // column groups (power of two)
   int kc;       // columns per thread, 1..16
@@ -94,10 +104,11 @@ struct LaunchIO {
 
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int sm_count(int device);
 
 // tuning knobs (env STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM; 0 = auto)
-struct Tuning { int threads = 0, stages = 0, ctas_per_sm = 0; };
+struct Tuning { int threads = 0, stages = 0, ctas_per_sm = 0, layout = kLayoutWarp, blocked = 0; };
 const Tuning& tuning();
 
 // relayout kernels (data.cu)

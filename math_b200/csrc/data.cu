@@ -14,37 +14,50 @@
 
 namespace stancuda {
 
-// staging chunk -> tiled X.  Chunk holds rows [0, n) x columns [c0, c0 + nc) of the block:
-//   column-major source: src[jj * src_ld + i]      (src_ld >= n)
-//   row-major source   : src[i * src_ld + c0 + jj] is NOT used; row-major chunks hold rows
-//                        [i0, i0 + ni) x all k columns: src[(i - i0) * src_ld + j]
+// Position of element (r, col) inside a tile, for either layout (common.cuh).
+struct TileMap {
+  int layout, R, C, kc, kpad;
+};
+__device__ __forceinline__ int64_t tile_elem_offset(const TileMap& m, int r, int col) {
+  if (m.layout == kLayoutCta) return int64_t(col) * m.R + r;
+  const int rpw = 32 / m.C;
+  const int w = r / rpw, rl = r - w * rpw;
+  const int cg = col / m.kc, j = col - cg * m.kc;
+  return int64_t(j * 8 + w) * 32 + rl * m.C + cg;
+}
+
+// staging chunk -> tiled X.  Column-major chunks hold rows [0, n) x columns [c0, c0 + nc) of the
+// block: src[jj * src_ld + i]; row-major chunks hold rows [i0, i0 + ni) x all k columns:
+// src[(i - i0) * src_ld + j].
 __global__ void retile_colmajor_kernel(const double* __restrict__ src, int64_t src_ld, int64_t n, int c0, int nc,
-                                       double* __restrict__ dst, int R, int kpad, int64_t tiles) {
-  const int64_t per_col = tiles * R;
+                                       double* __restrict__ dst, TileMap m, int64_t tiles) {
+  const int64_t per_col = tiles * m.R;
   const int64_t total = per_col * nc;
+  const int64_t tile_elems = int64_t(m.kpad) * m.R;
   for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < total;
        idx += int64_t(gridDim.x) * blockDim.x) {
     const int64_t jj = idx / per_col;
     const int64_t i = idx - jj * per_col;  // row index (padded range)
-    const int64_t tile = i / R;
-    const int r = int(i - tile * R);
+    const int64_t tile = i / m.R;
+    const int r = int(i - tile * m.R);
     const double v = i < n ? src[jj * src_ld + i] : 0.0;
-    dst[(tile * kpad + c0 + jj) * R + r] = v;
+    dst[tile * tile_elems + tile_elem_offset(m, r, int(c0 + jj))] = v;
   }
 }
 
 __global__ void retile_rowmajor_kernel(const double* __restrict__ src, int64_t src_ld, int64_t i0, int64_t ni,
-                                       int k, double* __restrict__ dst, int R, int kpad) {
-  // one thread per destination element of the row range; r fastest so writes coalesce
+                                       int k, double* __restrict__ dst, TileMap m) {
+  // one thread per destination element of the row range; r fastest
   const int64_t total = ni * k;
+  const int64_t tile_elems = int64_t(m.kpad) * m.R;
   for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < total;
        idx += int64_t(gridDim.x) * blockDim.x) {
     const int64_t j = idx / ni;
     const int64_t ii = idx - j * ni;
     const int64_t i = i0 + ii;
-    const int64_t tile = i / R;
-    const int r = int(i - tile * R);
-    dst[(tile * kpad + j) * R + r] = src[ii * src_ld + j];
+    const int64_t tile = i / m.R;
+    const int r = int(i - tile * m.R);
+    dst[tile * tile_elems + tile_elem_offset(m, r, int(j))] = src[ii * src_ld + j];
   }
 }
 
@@ -126,6 +139,7 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
   } while (0)
 
   const int blocks = sm_count(d->device) * 8;
+  const TileMap tmap{t.layout, t.R, t.C, t.kc, t.kpad};
   if (!x_row_major) {
     // chunk = a range of whole columns (rows row0 .. row0+n of each)
     int64_t cols_per_chunk = int64_t(kStageBytes / (size_t(n) * sizeof(double)));
@@ -148,8 +162,7 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
                                         size_t(ldx) * sizeof(double), size_t(n) * sizeof(double), size_t(nc),
                                         cudaMemcpyHostToDevice, stream));
       }
-      retile_colmajor_kernel<<<blocks, 256, 0, stream>>>(stage[which], n, n, int(c0), int(nc), d->x, t.R, t.kpad,
-                                                        t.tiles);
+      retile_colmajor_kernel<<<blocks, 256, 0, stream>>>(stage[which], n, n, int(c0), int(nc), d->x, tmap, t.tiles);
       SC_CUDA_CLEAN(cudaGetLastError());
       SC_CUDA_CLEAN(cudaEventRecord(freed[which], stream));
       up += uint64_t(nc) * n * sizeof(double);
@@ -171,7 +184,7 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
       const size_t cnt = size_t(ni - 1) * ldx + k;
       SC_CUDA_CLEAN(cudaMemcpyAsync(stage[which], x + size_t(row0 + i0) * ldx, cnt * sizeof(double),
                                     cudaMemcpyHostToDevice, stream));
-      retile_rowmajor_kernel<<<blocks, 256, 0, stream>>>(stage[which], ldx, i0, ni, int(k), d->x, t.R, t.kpad);
+      retile_rowmajor_kernel<<<blocks, 256, 0, stream>>>(stage[which], ldx, i0, ni, int(k), d->x, tmap);
       SC_CUDA_CLEAN(cudaGetLastError());
       SC_CUDA_CLEAN(cudaEventRecord(freed[which], stream));
       up += uint64_t(cnt) * sizeof(double);

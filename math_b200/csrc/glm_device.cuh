@@ -1,0 +1,318 @@
+// glm_device.cuh -- device-side pieces shared by the GLM kernels: kernel parameters, mbarrier / TMA
+// PTX helpers, the family epilogues, the two-level fixed-order final reduction and the all-reduce
+// over peer memory.
+#pragma once
+#include <math.h>
+
+#include "context.cuh"
+
+namespace stancuda {
+
+struct GlmKernelParams {
+  const double* x;
+  const void* y;
+  int64_t n;          // valid rows
+  int tiles;
+  int R, C, kc, kpad;
+  int log2R;
+  int stages;
+  int group_size;        // CTAs per reduction group (two-level final sum)
+  int blocked;           // warp kernel: 1 = CTA b owns tiles [b*per, (b+1)*per), 0 = round-robin
+  uint32_t stage_bytes;  // per stage in shared memory (tile + y, 128-aligned)
+  uint32_t tile_bytes;
+  uint32_t y_bytes;      // per tile
+  const double* params;
+  const double* alpha_vec;
+  const double* sigma_vec;
+  double* row_dalpha;
+  double* row_dsigma;
+  double* scratch;
+  unsigned int* ticket;
+  double* result;
+  uint32_t flags;
+  double lgamma_sum;
+  // all-reduce fused into the kernel (peer exchange over NVLink, comm.cu); world <= 1: off
+  int xchg_world, xchg_rank;
+  unsigned long long xchg_seq;
+  double* xchg_local;
+  double* xchg_peers[kXchgMaxWorld];
+#ifdef STAN_CUDA_PHASE_TIMERS
+  unsigned long long* timers;  // [grid][4] globaltimer stamps: start, first tile landed, loop end, CTA partial written; [grid*4] = end of last CTA
+#endif
+};
+
+int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, GlmKernelParams* p);
+
+// ---------------------------------------------------------------------------------------------
+// PTX helpers: mbarrier + 1-D TMA bulk copy (SASS: UBLKCP / SYNCS)
+// ---------------------------------------------------------------------------------------------
+#ifdef STAN_CUDA_PHASE_TIMERS
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned int smid() {
+  unsigned int v;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(v));
+  return v;
+}
+#define PHASE_STAMP(slot) do { if (tid == 0 && p.timers) { p.timers[size_t(blockIdx.x) * 4 + (slot)] = gtimer(); \
+  if ((slot) == 0) p.timers[4 * 2048 + 8 + blockIdx.x] = smid(); } } while (0)
+#else
+#define PHASE_STAMP(slot) do { } while (0)
+#endif
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
+                                             uint32_t bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1], %2, [%3], %4;" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// All-reduce of the result block fused into the kernel (replaces kernel -> ncclAllReduce).
+// Runs in the last CTA only.  fin[0..cols) holds this device's block on entry and the sum over
+// the world, added in rank order (bit-identical on every rank), on exit.
+//   push : fin -> slot [seq & 1][rank] of EVERY device's exchange block (stores to peer-mapped
+//          memory travel over NVLink), __threadfence_system, then one release-store of `seq` into
+//          that device's flag [seq & 1][rank];
+//   wait : acquire-loads of the world's flags in the own block until they show `seq`;
+//   sum  : system-scope loads of the world's slots in rank order.
+// Two slots suffice: a rank can be at most one collective ahead of the slowest rank, because it
+// cannot finish collective s before every rank has pushed its block of collective s.
+// A rank that does not show up within 30 s makes the result NaN (no hang).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(unsigned long long* ptr, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* ptr) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(ptr) : "memory");
+  return v;
+}
+__device__ __forceinline__ double ld_relaxed_sys(const double* ptr) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(ptr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+template <int THREADS, typename Sync>
+__device__ __forceinline__ void xchg_allreduce(const GlmKernelParams& p, double* fin, int cols, int tid,
+                                               int* s_flag, Sync sync) {
+  const int world = p.xchg_world, rank = p.xchg_rank;
+  const unsigned long long seq = p.xchg_seq;
+  const size_t slot = size_t(seq & 1ull) * world;
+  const size_t flag0 = size_t(2) * world * kXchgCols;  // flags follow the slots (as 8-byte words)
+  for (int idx = tid; idx < world * cols; idx += THREADS) {
+    const int q = idx / cols, c = idx - q * cols;
+    p.xchg_peers[q][(slot + rank) * kXchgCols + c] = fin[c];
+  }
+  __threadfence_system();
+  sync();
+  if (tid < world)
+    st_release_sys(reinterpret_cast<unsigned long long*>(p.xchg_peers[tid] + flag0) + slot + rank, seq);
+  if (tid == 0) *s_flag = 0;
+  sync();
+  if (tid < world) {
+    const unsigned long long* f = reinterpret_cast<const unsigned long long*>(p.xchg_local + flag0) + slot + tid;
+    const unsigned long long t0 = global_timer_ns();
+    while (ld_acquire_sys(f) != seq) {
+      if (global_timer_ns() - t0 > 30000000000ull) {
+        atomicExch(s_flag, 1);
+        break;
+      }
+    }
+  }
+  sync();
+  const bool timed_out = *s_flag != 0;
+  for (int c = tid; c < cols; c += THREADS) {
+    double sum = 0.0;
+    for (int q = 0; q < world; ++q) sum += ld_relaxed_sys(p.xchg_local + (slot + q) * kXchgCols + c);
+    fin[c] = timed_out ? __longlong_as_double(0x7ff8dead00000000ll) : sum;
+  }
+  sync();
+}
+
+// ---------------------------------------------------------------------------------------------
+// family epilogues: per-row log-likelihood terms and d = dL/deta, same expressions and the same
+// branch structure as the reference.
+// ---------------------------------------------------------------------------------------------
+struct RowTerms {
+  double d;   // derivative wrt the linear predictor
+  double t0;  // -> lp main term
+  double t2;  // normal: s^2
+};
+
+template <int FAMILY>
+__device__ __forceinline__ RowTerms row_epilogue(double eta, double alpha, double yv, double inv_sigma) {
+  RowTerms o;
+  if (FAMILY == STAN_CUDA_BERNOULLI_LOGIT) {
+    // bernoulli_logit_glm_lpmf.hpp:90-104,115-121 (cutoff = 20, the three-way select)
+    const double sign = 2.0 * yv - 1.0;
+    const double ytheta = sign * (eta + alpha);
+    const double e = exp(-ytheta);
+    o.t0 = ytheta > 20.0 ? -e : (ytheta < -20.0 ? ytheta : -log1p(e));
+    o.d = ytheta > 20.0 ? -e : (ytheta < -20.0 ? sign : sign * e / (e + 1.0));
+    o.t2 = 0.0;
+  } else if (FAMILY == STAN_CUDA_POISSON_LOG) {
+    // poisson_log_glm_lpmf.hpp:91-95,110-111
+    const double theta = eta + alpha;
+    const double e = exp(theta);
+    o.d = yv - e;
+    o.t0 = yv * theta - e;
+    o.t2 = 0.0;
+  } else {
+    // normal_id_glm_lpdf.hpp:108-117,138-141
+    const double s = (yv - eta - alpha) * inv_sigma;
+    o.d = inv_sigma * s;
+    o.t2 = s * s;
+    o.t0 = 0.0;
+  }
+  return o;
+}
+
+// ---------------------------------------------------------------------------------------------
+// End of kernel, after every CTA has written its (cols)-wide partial to p.scratch[blockIdx.x]:
+// two-level fixed-order reduction of the CTA partials, final scalars, optional all-reduce over
+// the devices, result block.  `sync` is the CTA-wide barrier of the NT participating threads.
+//   CTAs are grouped in blocks of `group_size` consecutive CTAs.  The last CTA of a group to
+//   finish adds the group's partials in CTA order; the last group to finish adds the group sums
+//   in group order.  The grouping depends on the grid only, so the result is bit-reproducible,
+//   and the critical path after the slowest CTA is two short sums instead of one of `grid` terms.
+// part: shared scratch of >= 4 doubles; fin: shared scratch of >= cols doubles; s_flag: shared int.
+// ---------------------------------------------------------------------------------------------
+template <int FAMILY, int NT, typename Sync>
+__device__ __forceinline__ void finish_reduction(const GlmKernelParams& p, int tid, int cols, double* part,
+                                                 double* fin, int* s_flag, Sync sync) {
+  const int grid = gridDim.x;
+  __threadfence();
+  sync();
+  PHASE_STAMP(3);
+  const int gsz = p.group_size, ngroups = (grid + gsz - 1) / gsz;
+  const int g = int(blockIdx.x) / gsz;
+  const int gfirst = g * gsz, glast = (gfirst + gsz < grid) ? gfirst + gsz : grid;
+  if (tid == 0) {
+    const unsigned int t = atomicAdd(p.ticket + 1 + g, 1u);
+    *s_flag = (t == unsigned(glast - gfirst) - 1u);
+  }
+  sync();
+  if (!*s_flag) return;
+  __threadfence();
+  double* gscratch = p.scratch + size_t(grid) * cols;  // [ngroups][cols]
+  for (int c = tid; c < cols; c += NT) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int b = gfirst;
+    for (; b + 4 <= glast; b += 4) {
+      s0 += __ldcg(p.scratch + size_t(b + 0) * cols + c);
+      s1 += __ldcg(p.scratch + size_t(b + 1) * cols + c);
+      s2 += __ldcg(p.scratch + size_t(b + 2) * cols + c);
+      s3 += __ldcg(p.scratch + size_t(b + 3) * cols + c);
+    }
+    for (; b < glast; ++b) s0 += __ldcg(p.scratch + size_t(b) * cols + c);
+    gscratch[size_t(g) * cols + c] = (s0 + s1) + (s2 + s3);
+  }
+  __threadfence();
+  sync();
+  if (tid == 0) {
+    p.ticket[1 + g] = 0u;  // every CTA of the group has taken its ticket: ready for the next launch
+    const unsigned int t = atomicAdd(p.ticket, 1u);
+    *s_flag = (t == unsigned(ngroups) - 1u);
+  }
+  sync();
+  if (!*s_flag) return;
+  __threadfence();
+  for (int c = tid; c < cols; c += NT) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int b = 0;
+    for (; b + 4 <= ngroups; b += 4) {
+      s0 += __ldcg(gscratch + size_t(b + 0) * cols + c);
+      s1 += __ldcg(gscratch + size_t(b + 1) * cols + c);
+      s2 += __ldcg(gscratch + size_t(b + 2) * cols + c);
+      s3 += __ldcg(gscratch + size_t(b + 3) * cols + c);
+    }
+    for (; b < ngroups; ++b) s0 += __ldcg(gscratch + size_t(b) * cols + c);
+    const double tot = (s0 + s1) + (s2 + s3);
+    if (c >= 4) fin[c] = tot;
+    else part[c] = tot;
+  }
+  sync();
+  if (tid == 0) {
+    const double A0 = part[0], A1 = part[1], A2 = part[2], A3 = part[3];
+    const double nn = double(p.n);
+    const double sigma0 = p.params[p.kpad + 1];
+    double lp = 0.0, dsig = 0.0, witness;
+    if (FAMILY == STAN_CUDA_BERNOULLI_LOGIT) {
+      if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
+      witness = A0;  // bernoulli_logit_glm_lpmf.hpp:106 tests logp
+    } else if (FAMILY == STAN_CUDA_POISSON_LOG) {
+      if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;  // :102-108
+      if (p.flags & STAN_CUDA_LP_MAIN) lp += A0;             // :109-112
+      witness = A1;  // poisson_log_glm_lpmf.hpp:97 tests sum(theta_derivative)
+    } else {
+      // normal_id_glm_lpdf.hpp:159-172
+      const double NEG_LOG_SQRT_TWO_PI = -0.91893853320467274178032973640561763986;
+      if (p.flags & STAN_CUDA_LP_CONST) lp += NEG_LOG_SQRT_TWO_PI * nn;
+      if (p.flags & STAN_CUDA_LP_SCALE) lp -= p.sigma_vec ? A3 : nn * log(sigma0);
+      if (p.flags & STAN_CUDA_LP_MAIN) lp -= 0.5 * A2;
+      if (!p.sigma_vec) dsig = (A2 - nn) * (1.0 / sigma0);  // :142-143
+      witness = A2;  // :150 tests y_scaled_sq_sum
+    }
+    fin[0] = lp;
+    fin[1] = A1;
+    fin[2] = dsig;
+    fin[3] = witness;
+    *p.ticket = 0u;  // ready for the next launch on this workspace (stream ordered)
+  }
+  sync();
+  // every term of the block is additive over row shards: sum it over the devices right here
+  if (p.xchg_world > 1) xchg_allreduce<NT>(p, fin, cols, tid, s_flag, sync);
+  for (int c = tid; c < cols; c += NT) p.result[c] = fin[c];
+#ifdef STAN_CUDA_PHASE_TIMERS
+  sync();
+  if (tid == 0 && p.timers) p.timers[size_t(grid) * 4] = gtimer();
+#endif
+}
+
+}  // namespace stancuda

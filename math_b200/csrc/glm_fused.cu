@@ -24,205 +24,9 @@
 //    CTA to finish (atomic ticket) adds the CTA partials in CTA order -> bit-reproducible.
 #include <math.h>
 
-#include "context.cuh"
+#include "glm_device.cuh"
 
 namespace stancuda {
-
-struct GlmKernelParams {
-  const double* x;
-  const void* y;
-  int64_t n;          // valid rows
-  int tiles;
-  int R, C, kc, kpad;
-  int log2R;
-  int stages;
-  int group_size;        // CTAs per reduction group (two-level final sum)
-  uint32_t stage_bytes;  // per stage in shared memory (tile + y, 128-aligned)
-  uint32_t tile_bytes;
-  uint32_t y_bytes;      // per tile
-  const double* params;
-  const double* alpha_vec;
-  const double* sigma_vec;
-  double* row_dalpha;
-  double* row_dsigma;
-  double* scratch;
-  unsigned int* ticket;
-  double* result;
-  uint32_t flags;
-  double lgamma_sum;
-  // all-reduce fused into the kernel (peer exchange over NVLink, comm.cu); world <= 1: off
-  int xchg_world, xchg_rank;
-  unsigned long long xchg_seq;
-  double* xchg_local;
-  double* xchg_peers[kXchgMaxWorld];
-#ifdef STAN_CUDA_PHASE_TIMERS
-  unsigned long long* timers;  // [grid][4] globaltimer stamps: start, first tile landed, loop end, CTA partial written; [grid*4] = end of last CTA
-#endif
-};
-
-// ---------------------------------------------------------------------------------------------
-// PTX helpers: mbarrier + 1-D TMA bulk copy (SASS: UBLKCP / SYNCS)
-// ---------------------------------------------------------------------------------------------
-#ifdef STAN_CUDA_PHASE_TIMERS
-__device__ __forceinline__ unsigned long long gtimer() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-#define PHASE_STAMP(slot) do { if (tid == 0 && p.timers) p.timers[size_t(blockIdx.x) * 4 + (slot)] = gtimer(); } while (0)
-#else
-#define PHASE_STAMP(slot) do { } while (0)
-#endif
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_fence_init() {
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t done;
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t"
-      "}"
-      : "=r"(done)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return done;
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
-}
-__device__ __forceinline__ uint64_t l2_evict_first_policy() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
-                                             uint32_t bar, uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
-      "[%0], [%1], %2, [%3], %4;" ::"r"(dst),
-      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
-      : "memory");
-}
-
-// ---------------------------------------------------------------------------------------------
-// All-reduce of the result block fused into the kernel (replaces kernel -> ncclAllReduce).
-// Runs in the last CTA only.  fin[0..cols) holds this device's block on entry and the sum over
-// the world, added in rank order (bit-identical on every rank), on exit.
-//   push : fin -> slot [seq & 1][rank] of EVERY device's exchange block (stores to peer-mapped
-//          memory travel over NVLink), __threadfence_system, then one release-store of `seq` into
-//          that device's flag [seq & 1][rank];
-//   wait : acquire-loads of the world's flags in the own block until they show `seq`;
-//   sum  : system-scope loads of the world's slots in rank order.
-// Two slots suffice: a rank can be at most one collective ahead of the slowest rank, because it
-// cannot finish collective s before every rank has pushed its block of collective s.
-// A rank that does not show up within 30 s makes the result NaN (no hang).
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_release_sys(unsigned long long* ptr, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* ptr) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(ptr) : "memory");
-  return v;
-}
-__device__ __forceinline__ double ld_relaxed_sys(const double* ptr) {
-  double v;
-  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(ptr) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-
-template <int THREADS>
-__device__ __forceinline__ void xchg_allreduce(const GlmKernelParams& p, double* fin, int cols, int tid,
-                                               int* s_flag) {
-  const int world = p.xchg_world, rank = p.xchg_rank;
-  const unsigned long long seq = p.xchg_seq;
-  const size_t slot = size_t(seq & 1ull) * world;
-  const size_t flag0 = size_t(2) * world * kXchgCols;  // flags follow the slots (as 8-byte words)
-  for (int idx = tid; idx < world * cols; idx += THREADS) {
-    const int q = idx / cols, c = idx - q * cols;
-    p.xchg_peers[q][(slot + rank) * kXchgCols + c] = fin[c];
-  }
-  __threadfence_system();
-  __syncthreads();
-  if (tid < world)
-    st_release_sys(reinterpret_cast<unsigned long long*>(p.xchg_peers[tid] + flag0) + slot + rank, seq);
-  if (tid == 0) *s_flag = 0;
-  __syncthreads();
-  if (tid < world) {
-    const unsigned long long* f = reinterpret_cast<const unsigned long long*>(p.xchg_local + flag0) + slot + tid;
-    const unsigned long long t0 = global_timer_ns();
-    while (ld_acquire_sys(f) != seq) {
-      if (global_timer_ns() - t0 > 30000000000ull) {
-        atomicExch(s_flag, 1);
-        break;
-      }
-    }
-  }
-  __syncthreads();
-  const bool timed_out = *s_flag != 0;
-  for (int c = tid; c < cols; c += THREADS) {
-    double sum = 0.0;
-    for (int q = 0; q < world; ++q) sum += ld_relaxed_sys(p.xchg_local + (slot + q) * kXchgCols + c);
-    fin[c] = timed_out ? __longlong_as_double(0x7ff8dead00000000ll) : sum;
-  }
-  __syncthreads();
-}
-
-// ---------------------------------------------------------------------------------------------
-// family epilogues: per-row log-likelihood terms and d = dL/deta, same expressions and the same
-// branch structure as the reference.
-// ---------------------------------------------------------------------------------------------
-struct RowTerms {
-  double d;   // derivative wrt the linear predictor
-  double t0;  // -> lp main term
-  double t2;  // normal: s^2
-};
-
-template <int FAMILY>
-__device__ __forceinline__ RowTerms row_epilogue(double eta, double alpha, double yv, double inv_sigma) {
-  RowTerms o;
-  if (FAMILY == STAN_CUDA_BERNOULLI_LOGIT) {
-    // bernoulli_logit_glm_lpmf.hpp:90-104,115-121 (cutoff = 20, the three-way select)
-    const double sign = 2.0 * yv - 1.0;
-    const double ytheta = sign * (eta + alpha);
-    const double e = exp(-ytheta);
-    o.t0 = ytheta > 20.0 ? -e : (ytheta < -20.0 ? ytheta : -log1p(e));
-    o.d = ytheta > 20.0 ? -e : (ytheta < -20.0 ? sign : sign * e / (e + 1.0));
-    o.t2 = 0.0;
-  } else if (FAMILY == STAN_CUDA_POISSON_LOG) {
-    // poisson_log_glm_lpmf.hpp:91-95,110-111
-    const double theta = eta + alpha;
-    const double e = exp(theta);
-    o.d = yv - e;
-    o.t0 = yv * theta - e;
-    o.t2 = 0.0;
-  } else {
-    // normal_id_glm_lpdf.hpp:108-117,138-141
-    const double s = (yv - eta - alpha) * inv_sigma;
-    o.d = inv_sigma * s;
-    o.t2 = s * s;
-    o.t0 = 0.0;
-  }
-  return o;
-}
 
 // Sum `v` over the `width` consecutive lanes that share a column group (width = min(R, 32)).
 __device__ __forceinline__ double group_reduce(double v, int width) {
@@ -403,97 +207,9 @@ glm_fused_kernel(const GlmKernelParams p) {
     my_scratch[c] = sum;
   }
 
-  // ---- two-level fixed-order reduction of the CTA partials -----------------------------------
-  // CTAs are grouped in blocks of `gsz` consecutive CTAs.  The last CTA of a group to finish adds
-  // the group's partials in CTA order; the last group to finish adds the group sums in group
-  // order.  The grouping depends on the grid only, so the result is bit-reproducible, and the
-  // critical path after the slowest CTA is two short (<= ~25 term) sums instead of one of `grid`.
-  __threadfence();
-  __syncthreads();
-  PHASE_STAMP(3);
-  const int gsz = p.group_size, ngroups = (grid + gsz - 1) / gsz;
-  const int g = int(blockIdx.x) / gsz;
-  const int gfirst = g * gsz, glast = (gfirst + gsz < grid) ? gfirst + gsz : grid;
-  if (tid == 0) {
-    const unsigned int t = atomicAdd(p.ticket + 1 + g, 1u);
-    s_is_last = (t == unsigned(glast - gfirst) - 1u);
-  }
-  __syncthreads();
-  if (!s_is_last) return;
-  __threadfence();
-  double* gscratch = p.scratch + size_t(grid) * cols;  // [ngroups][cols]
-  for (int c = tid; c < cols; c += THREADS) {
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int b = gfirst;
-    for (; b + 4 <= glast; b += 4) {
-      s0 += __ldcg(p.scratch + size_t(b + 0) * cols + c);
-      s1 += __ldcg(p.scratch + size_t(b + 1) * cols + c);
-      s2 += __ldcg(p.scratch + size_t(b + 2) * cols + c);
-      s3 += __ldcg(p.scratch + size_t(b + 3) * cols + c);
-    }
-    for (; b < glast; ++b) s0 += __ldcg(p.scratch + size_t(b) * cols + c);
-    gscratch[size_t(g) * cols + c] = (s0 + s1) + (s2 + s3);
-  }
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    p.ticket[1 + g] = 0u;  // every CTA of the group has taken its ticket: ready for the next launch
-    const unsigned int t = atomicAdd(p.ticket, 1u);
-    s_is_last = (t == unsigned(ngroups) - 1u);
-  }
-  __syncthreads();
-  if (!s_is_last) return;
-  __threadfence();
+  // ---- two-level fixed-order reduction of the CTA partials, finalisation, all-reduce ----------
   double* fin = reinterpret_cast<double*>(stage0);  // [cols]; every stage has been consumed by now
-  for (int c = tid; c < cols; c += THREADS) {
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int b = 0;
-    for (; b + 4 <= ngroups; b += 4) {
-      s0 += __ldcg(gscratch + size_t(b + 0) * cols + c);
-      s1 += __ldcg(gscratch + size_t(b + 1) * cols + c);
-      s2 += __ldcg(gscratch + size_t(b + 2) * cols + c);
-      s3 += __ldcg(gscratch + size_t(b + 3) * cols + c);
-    }
-    for (; b < ngroups; ++b) s0 += __ldcg(gscratch + size_t(b) * cols + c);
-    const double tot = (s0 + s1) + (s2 + s3);
-    if (c >= 4) fin[c] = tot;
-    else part[c] = tot;
-  }
-  __syncthreads();
-  if (tid == 0) {
-    const double A0 = part[0], A1 = part[1], A2 = part[2], A3 = part[3];
-    const double nn = double(p.n);
-    double lp = 0.0, dsig = 0.0, witness;
-    if (FAMILY == STAN_CUDA_BERNOULLI_LOGIT) {
-      if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
-      witness = A0;  // bernoulli_logit_glm_lpmf.hpp:106 tests logp
-    } else if (FAMILY == STAN_CUDA_POISSON_LOG) {
-      if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;  // :102-108
-      if (p.flags & STAN_CUDA_LP_MAIN) lp += A0;             // :109-112
-      witness = A1;  // poisson_log_glm_lpmf.hpp:97 tests sum(theta_derivative)
-    } else {
-      // normal_id_glm_lpdf.hpp:159-172
-      const double NEG_LOG_SQRT_TWO_PI = -0.91893853320467274178032973640561763986;
-      if (p.flags & STAN_CUDA_LP_CONST) lp += NEG_LOG_SQRT_TWO_PI * nn;
-      if (p.flags & STAN_CUDA_LP_SCALE) lp -= p.sigma_vec ? A3 : nn * log(sigma0);
-      if (p.flags & STAN_CUDA_LP_MAIN) lp -= 0.5 * A2;
-      if (!p.sigma_vec) dsig = (A2 - nn) * inv_sigma0;  // :142-143
-      witness = A2;  // :150 tests y_scaled_sq_sum
-    }
-    fin[0] = lp;
-    fin[1] = A1;
-    fin[2] = dsig;
-    fin[3] = witness;
-    *p.ticket = 0u;  // ready for the next launch on this workspace (stream ordered)
-  }
-  __syncthreads();
-  // every term of the block is additive over row shards: sum it over the devices right here
-  if (p.xchg_world > 1) xchg_allreduce<THREADS>(p, fin, cols, tid, &s_is_last);
-  for (int c = tid; c < cols; c += THREADS) p.result[c] = fin[c];
-#ifdef STAN_CUDA_PHASE_TIMERS
-  __syncthreads();
-  if (tid == 0 && p.timers) p.timers[size_t(grid) * 4] = gtimer();
-#endif
+  finish_reduction<FAMILY, THREADS>(p, tid, cols, part, fin, &s_is_last, [] { __syncthreads(); });
 }
 
 }  // namespace stancuda
@@ -515,6 +231,10 @@ static Tuning& tuning_mut() {
     u.threads = env_int("STAN_CUDA_THREADS", 0);
     u.stages = env_int("STAN_CUDA_STAGES", 0);
     u.ctas_per_sm = env_int("STAN_CUDA_CTAS_PER_SM", 0);
+    const char* sv = getenv("STAN_CUDA_SCHEDULE");
+    u.blocked = (sv && (sv[0] == 'b' || sv[0] == 'B')) ? 1 : 0;
+    const char* kv = getenv("STAN_CUDA_KERNEL");
+    u.layout = (kv && (kv[0] == 'c' || kv[0] == 'C')) ? kLayoutCta : kLayoutWarp;
     return u;
   }();
   return t;
@@ -534,6 +254,22 @@ int sm_count(int device) {
 }
 
 bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t) {
+  if (k < 1) k = 1;
+  if (tuning().layout == kLayoutWarp) {
+    // 8 consumer warps of 32 lanes; smallest power-of-two C <= 32 with at most kMaxKc columns per lane
+    int C = 1;
+    while ((k + C - 1) / C > kMaxKc) C *= 2;
+    if (C > 32) return false;  // k > 512: outside the fused kernel
+    t->layout = kLayoutWarp;
+    t->threads = 256;
+    t->C = C;
+    t->kc = int((k + C - 1) / C);
+    t->R = 256 / C;
+    t->kpad = C * t->kc;
+    t->tiles = (n + t->R - 1) / t->R;
+    return true;
+  }
+  t->layout = kLayoutCta;
   int threads = threads_override ? threads_override : tuning().threads;
   if (threads != 128 && threads != 256 && threads != 512) threads = 256;
   if (k < 1) k = 1;
@@ -598,8 +334,53 @@ static size_t smem_bytes(const Tiling& t, int stages, size_t* stage_bytes_out) {
 static unsigned long long* g_phase_timers = nullptr;  // debugging build only (tools/phase_timers.py)
 #endif
 
+// Everything of the kernel parameter block that does not depend on the kernel variant.
+int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, GlmKernelParams* p) {
+  const Tiling& t = d->t;
+  p->stages = 0;
+  p->group_size = 1;
+  p->stage_bytes = 0;
+  p->blocked = 0;
+  p->x = d->x;
+  p->y = d->y;
+  p->n = d->n;
+  p->tiles = int(t.tiles);
+  p->R = t.R; p->C = t.C; p->kc = t.kc; p->kpad = t.kpad;
+  p->log2R = 0;
+  while ((1 << p->log2R) < t.R) ++p->log2R;
+  p->tile_bytes = uint32_t(t.tile_bytes());
+  p->y_bytes = uint32_t(size_t(t.R) * (d->y_is_double ? sizeof(double) : sizeof(int)));
+  p->params = io.d_params;
+  p->alpha_vec = io.d_alpha_vec;
+  p->sigma_vec = io.d_sigma_vec;
+  p->row_dalpha = io.d_row_dalpha;
+  p->row_dsigma = io.d_row_dsigma;
+  p->scratch = ws->scratch;
+  p->ticket = ws->ticket;
+  p->result = io.d_result;
+  p->flags = io.flags;
+  p->lgamma_sum = d->lgamma_sum;
+  p->xchg_world = 0;
+  p->xchg_rank = 0;
+  p->xchg_seq = io.xchg_seq;
+  p->xchg_local = nullptr;
+  for (int q = 0; q < kXchgMaxWorld; ++q) p->xchg_peers[q] = nullptr;
+  if (io.xchg && io.xchg->world > 1) {
+    if (t.kpad + 4 > kXchgCols) return fail(STAN_CUDA_ERR_ARG, "launch_glm: result block exceeds the exchange slot");
+    p->xchg_world = io.xchg->world;
+    p->xchg_rank = io.xchg->rank;
+    p->xchg_local = io.xchg->local;
+    for (int q = 0; q < io.xchg->world; ++q) p->xchg_peers[q] = io.xchg->peers[q];
+  }
+#ifdef STAN_CUDA_PHASE_TIMERS
+  p->timers = g_phase_timers;
+#endif
+  return STAN_CUDA_OK;
+}
+
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
+  if (t.layout == kLayoutWarp) return launch_glm_warp(d, io, ws, stream);
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
   const int sms = sm_count(d->device);
   int ctas_per_sm = tuning().ctas_per_sm;
@@ -626,43 +407,10 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
   SC_TRY(workspace_reserve(ws, d->device, size_t(grid + ngroups) * (t.kpad + 4)));
 
   GlmKernelParams p;
-  p.x = d->x;
-  p.y = d->y;
-  p.n = d->n;
-  p.tiles = int(t.tiles);
-  p.R = t.R; p.C = t.C; p.kc = t.kc; p.kpad = t.kpad;
-  p.log2R = 0;
-  while ((1 << p.log2R) < t.R) ++p.log2R;
+  SC_TRY(fill_kernel_params(d, io, ws, &p));
   p.stages = stages;
   p.group_size = group_size;
   p.stage_bytes = uint32_t(stage_bytes);
-  p.tile_bytes = uint32_t(t.tile_bytes());
-  p.y_bytes = uint32_t(size_t(t.R) * (d->y_is_double ? sizeof(double) : sizeof(int)));
-  p.params = io.d_params;
-  p.alpha_vec = io.d_alpha_vec;
-  p.sigma_vec = io.d_sigma_vec;
-  p.row_dalpha = io.d_row_dalpha;
-  p.row_dsigma = io.d_row_dsigma;
-  p.scratch = ws->scratch;
-  p.ticket = ws->ticket;
-  p.result = io.d_result;
-  p.flags = io.flags;
-  p.lgamma_sum = d->lgamma_sum;
-  p.xchg_world = 0;
-  p.xchg_rank = 0;
-  p.xchg_seq = io.xchg_seq;
-  p.xchg_local = nullptr;
-  for (int q = 0; q < kXchgMaxWorld; ++q) p.xchg_peers[q] = nullptr;
-  if (io.xchg && io.xchg->world > 1) {
-    if (t.kpad + 4 > kXchgCols) return fail(STAN_CUDA_ERR_ARG, "launch_glm: result block exceeds the exchange slot");
-    p.xchg_world = io.xchg->world;
-    p.xchg_rank = io.xchg->rank;
-    p.xchg_local = io.xchg->local;
-    for (int q = 0; q < io.xchg->world; ++q) p.xchg_peers[q] = io.xchg->peers[q];
-  }
-#ifdef STAN_CUDA_PHASE_TIMERS
-  p.timers = g_phase_timers;
-#endif
   const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
   switch (d->family) {
     case STAN_CUDA_BERNOULLI_LOGIT:
@@ -682,6 +430,10 @@ extern "C" STAN_CUDA_API void stan_cuda_debug_set_timers(unsigned long long* dev
   stancuda::g_phase_timers = device_buf;
 }
 #endif
+
+extern "C" void stan_cuda_set_kernel(int variant) {
+  stancuda::tuning_mut().layout = variant == 0 ? stancuda::kLayoutCta : stancuda::kLayoutWarp;
+}
 
 extern "C" void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm) {
   stancuda::Tuning& t = stancuda::tuning_mut();

@@ -1,0 +1,296 @@
+// glm_warp.cu -- warp-synchronous variant of the fused GLM value+gradient kernel (sm_100a, FP64).
+//
+// Same contract as glm_fused.cu (one pass over X: eta = X*beta + alpha, per-row log-likelihood,
+// d = dL/deta, g = X^T d;  bernoulli_logit_glm_lpmf.hpp:88-135, poisson_log_glm_lpmf.hpp:91-129,
+// normal_id_glm_lpdf.hpp:100-172), different decomposition:
+//
+//  * a CTA is 8 warps.  Every stage of the TMA ring has a "full" mbarrier (cp.async.bulk
+//    complete_tx) and an arrival counter in shared memory: a warp bumps the counter once its part
+//    of the tile sits in registers, and the LAST warp to do so re-arms the stage with the tile
+//    `stages` ahead -- the earliest possible moment, and no warp ever waits for another one.
+//    There is NO CTA-wide barrier in the tile loop.  (Tried and dropped: a dedicated producer warp
+//    -- 288 threads x 2 CTAs leave 112 registers per thread and the 48 live doubles spill; a fixed
+//    producer lane in warp 0 -- CTAs whose warp 0 fell behind degenerated to one tile in flight and
+//    ran 2x slower than the rest.)
+//  * all C column groups of a row live in ONE warp: lane = row_in_warp * C + column_group.  The
+//    partial dot products meet through log2(C) xor-shuffles (every lane of the row ends up with the
+//    bit-identical eta), every lane runs the family epilogue for its row, and goes straight on
+//    to its 16 gradient FMAs.  Warps never wait for each other, so the long dependent FP64 chains of
+//    the epilogues (exp / log1p / division) of 16 resident warps overlap each other and the loads;
+//    in glm_fused.cu one owner warp per CTA ran the epilogue while the other seven sat at a barrier.
+//  * tile layout in HBM (see data.cu): x_dev[tile][j][warp][lane], so the j-th load of a warp is one
+//    contiguous 256-byte shared-memory read, conflict-free.
+//  * reductions are fixed-order (shuffle trees, then warps in order, then finish_reduction):
+//    results are bit-reproducible.
+#include "glm_device.cuh"
+
+namespace stancuda {
+
+constexpr int kWarpConsumers = 8;                 // warps per CTA
+constexpr int kWarpThreads = kWarpConsumers * 32;
+
+__device__ __forceinline__ void consumer_sync() { __syncthreads(); }
+
+template <int FAMILY, bool ROWIO>
+__global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKernelParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  constexpr int NT = kWarpConsumers * 32;
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int C = p.C, kc = p.kc, kpad = p.kpad, R = p.R;
+  const int rpw = 32 / C;  // rows per warp
+  const int cg = lane & (C - 1);
+  const int rl = lane / C;
+
+  unsigned char* stage0 = smem;
+  double* red = reinterpret_cast<double*>(smem + size_t(p.stages) * p.stage_bytes);  // [WARPS][kpad + 4]
+  double* part = red + size_t(kWarpConsumers) * (kpad + 4);                          // [8]
+  uint64_t* full = reinterpret_cast<uint64_t*>(part + 8);                            // [stages]
+  int* arrived = reinterpret_cast<int*>(full + p.stages);                            // [stages]
+  __shared__ int s_flag;
+
+  const int grid = gridDim.x;
+  // static tile schedule: blocked (CTA b owns a contiguous run of tiles) or round-robin
+  const int per = (p.tiles + grid - 1) / grid;
+  const int64_t tile0 = p.blocked ? int64_t(blockIdx.x) * per : int64_t(blockIdx.x);
+  const int64_t tstride = p.blocked ? 1 : grid;
+  int ntl;  // tiles of this CTA
+  if (p.blocked) {
+    const int64_t left = int64_t(p.tiles) - tile0;
+    ntl = left <= 0 ? 0 : (left < per ? int(left) : per);
+  } else {
+    ntl = (p.tiles - int(blockIdx.x) + grid - 1) / grid;
+  }
+
+  PHASE_STAMP(0);
+  if (tid == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(smem_u32(&full[s]), 1);
+      arrived[s] = 0;
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  // ---- producer role: lane 0 of warp 0 ------------------------------------------------------------
+  const uint32_t tx_bytes = p.tile_bytes + p.y_bytes;
+  const unsigned char* xbytes = reinterpret_cast<const unsigned char*>(p.x);
+  const unsigned char* ybytes = reinterpret_cast<const unsigned char*>(p.y);
+  uint64_t policy = 0;
+  auto issue = [&](int t) {  // stage tile number t of this CTA
+    const int s = t % p.stages;
+    const int64_t tile = tile0 + int64_t(t) * tstride;
+    const uint32_t bar = smem_u32(&full[s]);
+    const uint32_t dst = smem_u32(stage0 + size_t(s) * p.stage_bytes);
+    mbar_expect_tx(bar, tx_bytes);
+    tma_bulk_g2s(dst, xbytes + tile * p.tile_bytes, p.tile_bytes, bar, policy);
+    tma_bulk_g2s(dst + p.tile_bytes, ybytes + tile * p.y_bytes, p.y_bytes, bar, policy);
+  };
+  if (lane == 0) policy = l2_evict_first_policy();
+  if (tid == 0) {
+    const int pre = ntl < p.stages ? ntl : p.stages;
+    for (int t = 0; t < pre; ++t) issue(t);
+  }
+
+  // ---- consumer warps --------------------------------------------------------------------------
+  double bj[kMaxKc], acc[kMaxKc];
+#pragma unroll
+  for (int j = 0; j < kMaxKc; ++j) {
+    bj[j] = j < kc ? p.params[cg * kc + j] : 0.0;
+    acc[j] = 0.0;
+  }
+  const double alpha0 = p.params[kpad];
+  const double sigma0 = p.params[kpad + 1];
+  const double inv_sigma0 = FAMILY == STAN_CUDA_NORMAL_ID ? 1.0 / sigma0 : 1.0;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // lp main, sum d, sum s^2, sum log sigma (cg == 0 lanes)
+  const int r_in_tile = warp * rpw + rl;
+
+  for (int it = 0; it < ntl; ++it) {
+    const int s = it % p.stages;
+    const int64_t tile = tile0 + int64_t(it) * tstride;
+    const int64_t row = tile * R + r_in_tile;
+    mbar_wait(smem_u32(&full[s]), (it / p.stages) & 1);
+#ifdef STAN_CUDA_PHASE_TIMERS
+    if (it == 0) PHASE_STAMP(1);
+    if (p.timers && (it & 7) == 0 && (it >> 3) < 32 && lane == 0 && (warp == 0 || warp == 7))
+      p.timers[8 * 2048 + (size_t(blockIdx.x) * 2 + (warp == 7)) * 32 + (it >> 3)] = gtimer();
+#endif
+    const unsigned char* st = stage0 + size_t(s) * p.stage_bytes;
+    const double* xs = reinterpret_cast<const double*>(st) + warp * 32 + lane;
+    double xr[kMaxKc];
+#pragma unroll
+    for (int j = 0; j < kMaxKc; ++j) xr[j] = j < kc ? xs[j * NT] : 0.0;
+    double yv;
+    if (FAMILY == STAN_CUDA_NORMAL_ID) {
+      yv = reinterpret_cast<const double*>(st + p.tile_bytes)[r_in_tile];
+    } else {
+      yv = double(reinterpret_cast<const int*>(st + p.tile_bytes)[r_in_tile]);
+    }
+
+    double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < kMaxKc; j += 2) {
+      p0 = fma(xr[j], bj[j], p0);
+      p1 = fma(xr[j + 1], bj[j + 1], p1);
+    }
+    double eta = p0 + p1;
+    // this warp's part of the tile sits in registers: count it; the last warp re-arms the stage
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence_block();
+      if (atomicAdd(&arrived[s], 1) == kWarpConsumers - 1) {
+        arrived[s] = 0;  // the next arrivals on this stage come only after the refill below has landed
+        __threadfence_block();
+        if (it + p.stages < ntl) issue(it + p.stages);
+      }
+    }
+
+    // partial dots of the C column groups of a row: xor butterfly, identical result in every lane
+    for (int off = 1; off < C; off <<= 1) eta += __shfl_xor_sync(0xffffffffu, eta, off);
+
+    double alpha = alpha0, inv_sigma = inv_sigma0, sigma_row = sigma0;
+    const bool valid = row < p.n;
+    if (ROWIO && valid) {
+      if (p.alpha_vec) alpha = p.alpha_vec[row];
+      if (FAMILY == STAN_CUDA_NORMAL_ID && p.sigma_vec) {
+        sigma_row = p.sigma_vec[row];
+        inv_sigma = 1.0 / sigma_row;
+      }
+    }
+    const RowTerms o = row_epilogue<FAMILY>(eta, alpha, yv, inv_sigma);
+    const double d = valid ? o.d : 0.0;
+    if (valid && cg == 0) {
+      a0 += o.t0;
+      a1 += o.d;
+      a2 += o.t2;
+      if (ROWIO) {
+        if (FAMILY == STAN_CUDA_NORMAL_ID && p.sigma_vec) {
+          a3 += log(sigma_row);
+          if (p.row_dsigma) p.row_dsigma[row] = (o.t2 - 1.0) * inv_sigma;
+        }
+        if (p.row_dalpha) p.row_dalpha[row] = o.d;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kMaxKc; ++j) acc[j] = fma(xr[j], d, acc[j]);
+  }
+
+  PHASE_STAMP(2);
+  // ---- CTA reduction: rows of a warp (xor offsets C .. 16), then the 8 warps in order ----------
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+#pragma unroll
+    for (int j = 0; j < kMaxKc; ++j) {
+      const double o = __shfl_xor_sync(0xffffffffu, acc[j], off);
+      if (off >= C) acc[j] += o;
+    }
+    const double o0 = __shfl_xor_sync(0xffffffffu, a0, off), o1 = __shfl_xor_sync(0xffffffffu, a1, off);
+    const double o2 = __shfl_xor_sync(0xffffffffu, a2, off), o3 = __shfl_xor_sync(0xffffffffu, a3, off);
+    if (off >= C) {
+      a0 += o0;
+      a1 += o1;
+      a2 += o2;
+      a3 += o3;
+    }
+  }
+  const int cols = kpad + 4;
+  double* myred = red + size_t(warp) * cols;
+  if (rl == 0) {  // lanes 0 .. C-1 hold the sums of column group cg = lane
+#pragma unroll
+    for (int j = 0; j < kMaxKc; ++j)
+      if (j < kc) myred[4 + cg * kc + j] = acc[j];
+    if (cg == 0) {
+      myred[0] = a0;
+      myred[1] = a1;
+      myred[2] = a2;
+      myred[3] = a3;
+    }
+  }
+  consumer_sync();
+  double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
+  for (int c = tid; c < cols; c += NT) {
+    double sum = 0.0;
+#pragma unroll
+    for (int w = 0; w < kWarpConsumers; ++w) sum += red[size_t(w) * cols + c];
+    my_scratch[c] = sum;
+  }
+  double* fin = reinterpret_cast<double*>(stage0);  // [cols]; every stage has been consumed by now
+  finish_reduction<FAMILY, NT>(p, tid, cols, part, fin, &s_flag, [] { consumer_sync(); });
+}
+
+// =============================================================================================
+// host side
+// =============================================================================================
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static size_t warp_smem_bytes(const Tiling& t, int stages, size_t* stage_bytes_out) {
+  const size_t stage = align_up(t.tile_bytes() + size_t(t.R) * sizeof(double), 128);
+  if (stage_bytes_out) *stage_bytes_out = stage;
+  const size_t fixed = (size_t(kWarpConsumers) * (t.kpad + 4) + 8) * sizeof(double) + size_t(stages) * (sizeof(uint64_t) + sizeof(int)) + 8;
+  return size_t(stages) * stage + fixed;
+}
+
+template <int FAMILY, bool ROWIO>
+static int launch_warp_inst(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
+  auto kern = glm_warp_kernel<FAMILY, ROWIO>;
+  static std::atomic<size_t> configured[64];
+  int dev = 0;
+  SC_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && configured[dev].load(std::memory_order_relaxed) < smem) {
+    SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    configured[dev].store(smem, std::memory_order_relaxed);
+  }
+  kern<<<grid, kWarpThreads, smem, stream>>>(p);
+  SC_CUDA(cudaGetLastError());
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
+  return STAN_CUDA_OK;
+}
+
+int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
+  const Tiling& t = d->t;
+  if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
+  const int sms = sm_count(d->device);
+  int ctas_per_sm = tuning().ctas_per_sm;
+  if (ctas_per_sm <= 0 || ctas_per_sm > 2) ctas_per_sm = 2;
+  const size_t budget = (size_t(228) * 1024) / ctas_per_sm - 1024 - 64;
+  int stages = tuning().stages;
+  size_t stage_bytes = 0;
+  if (stages <= 0) {
+    stages = 6;
+    while (stages > 2 && warp_smem_bytes(t, stages, nullptr) > budget) --stages;
+  }
+  size_t smem = warp_smem_bytes(t, stages, &stage_bytes);
+  while (stages > 1 && smem > size_t(227) * 1024) smem = warp_smem_bytes(t, --stages, &stage_bytes);
+  if (smem > size_t(227) * 1024) return fail(STAN_CUDA_ERR_ARG, "launch_glm: tile does not fit shared memory");
+
+  int64_t grid64 = int64_t(sms) * ctas_per_sm;
+  if (grid64 > t.tiles) grid64 = t.tiles;
+  const int grid = int(grid64);
+  int group_size = 1;
+  while (group_size * group_size < grid) ++group_size;
+  const int ngroups = (grid + group_size - 1) / group_size;
+  if (ngroups > 60) return fail(STAN_CUDA_ERR_ARG, "launch_glm: grid too large for the ticket block");
+  SC_TRY(workspace_reserve(ws, d->device, size_t(grid + ngroups) * (t.kpad + 4)));
+
+  GlmKernelParams p;
+  SC_TRY(fill_kernel_params(d, io, ws, &p));
+  p.stages = stages;
+  p.group_size = group_size;
+  p.stage_bytes = uint32_t(stage_bytes);
+  p.blocked = tuning().blocked;
+  const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
+  switch (d->family) {
+    case STAN_CUDA_BERNOULLI_LOGIT:
+      return rowio ? launch_warp_inst<STAN_CUDA_BERNOULLI_LOGIT, true>(p, grid, smem, stream)
+                   : launch_warp_inst<STAN_CUDA_BERNOULLI_LOGIT, false>(p, grid, smem, stream);
+    case STAN_CUDA_POISSON_LOG:
+      return rowio ? launch_warp_inst<STAN_CUDA_POISSON_LOG, true>(p, grid, smem, stream)
+                   : launch_warp_inst<STAN_CUDA_POISSON_LOG, false>(p, grid, smem, stream);
+    case STAN_CUDA_NORMAL_ID:
+      return rowio ? launch_warp_inst<STAN_CUDA_NORMAL_ID, true>(p, grid, smem, stream)
+                   : launch_warp_inst<STAN_CUDA_NORMAL_ID, false>(p, grid, smem, stream);
+  }
+  return fail(STAN_CUDA_ERR_ARG, "launch_glm: unknown family");
+}
+
+}  // namespace stancuda

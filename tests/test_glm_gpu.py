@@ -10,11 +10,17 @@ from tests.helpers import RTOL, assert_close, check_glm_result, glm_case, normal
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def glm():
+@pytest.fixture(scope="module", params=["warp", "cta"])
+def glm(request):
+    """The whole module runs once per kernel variant (csrc/glm_warp.cu, csrc/glm_fused.cu)."""
     from math_b200 import glm as g
+    from math_b200._lib import lib
     g.init(1)
-    return g
+    g.cache_clear()
+    lib().stan_cuda_set_kernel(1 if request.param == "warp" else 0)
+    yield g
+    g.cache_clear()
+    lib().stan_cuda_set_kernel(1)
 
 
 @pytest.fixture(scope="module")

@@ -1,0 +1,67 @@
+#!/usr/bin/env python
+"""A/B of the two kernel variants (warp | cta) over a list of shapes, CUDA-event timed, inputs
+resident and larger than L2.  One JSON line per (kernel, shape)."""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+SHAPES = [("poisson_log", 10_000_000, 128), ("poisson_log", 1_250_000, 128), ("bernoulli_logit", 1_000_000, 32),
+          ("bernoulli_logit", 1_250_000, 128), ("normal_id", 2_500_000, 256), ("normal_id", 1_000_000, 32),
+          ("bernoulli_logit", 100_000, 32)]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=30)
+    ap.add_argument("--kernels", default="warp,cta")
+    ap.add_argument("--stages", type=int, default=0)
+    ap.add_argument("--ctas", type=int, default=0)
+    ap.add_argument("--shapes", default="")
+    args = ap.parse_args()
+    import torch
+    from bench import FAM_ID, measured_peak, synth_shard
+    from math_b200 import glm
+    from math_b200._lib import lib
+    glm.init(1)
+    peak, _ = measured_peak()
+    shapes = SHAPES
+    if args.shapes:
+        shapes = [(f, int(n), int(k)) for f, n, k in (sh.split(":") for sh in args.shapes.split(","))]
+    stream = torch.cuda.Stream()
+    for family, n, k in shapes:
+        x, y, alpha, beta, sigma = synth_shard(family, n, k, seed=1)
+        fam = FAM_ID[family]
+        flags = glm.glm_flags(fam, False)
+        for kern in args.kernels.split(","):
+            lib().stan_cuda_set_kernel(1 if kern == "warp" else 0)
+            lib().stan_cuda_set_tuning(0, args.stages, args.ctas)
+            data = glm.GlmData(fam, x, y)
+            params = np.zeros(data.params_len)
+            params[:k], params[data.kpad], params[data.kpad + 1] = beta, alpha[0], 1.0
+            dp = torch.from_numpy(params).cuda()
+            dr = torch.zeros(data.result_len, dtype=torch.float64, device="cuda")
+            with torch.cuda.stream(stream):
+                for _ in range(5):
+                    data.launch(flags, dp.data_ptr(), dr.data_ptr(), stream.cuda_stream)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(args.reps):
+                    data.launch(flags, dp.data_ptr(), dr.data_ptr(), stream.cuda_stream)
+                e1.record(stream)
+            stream.synchronize()
+            ms = e0.elapsed_time(e1) / args.reps
+            gbs = data.algorithmic_bytes / (ms * 1e-3) / 1e9
+            print(json.dumps({"kernel": kern, "family": family, "n": n, "k": k, "us": round(ms * 1e3, 2),
+                              "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "lp": float(dr[0])}), flush=True)
+            data.close()
+        del x, y
+
+
+if __name__ == "__main__":
+    main()

@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--family", default="bernoulli_logit")
     ap.add_argument("--n", type=int, default=1_000_000)
     ap.add_argument("--k", type=int, default=32)
+    ap.add_argument("--kernel", default="warp", choices=["warp", "cta"])
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--threads", type=int, default=0)
     ap.add_argument("--stages", type=int, default=0)
@@ -34,6 +35,7 @@ def main():
     from math_b200 import glm
     glm.init(1)
     _lib.lib().stan_cuda_set_tuning(args.threads, args.stages, args.ctas)
+    _lib.lib().stan_cuda_set_kernel(1 if args.kernel == "warp" else 0)
     x, y, alpha, beta, sigma = synth_shard(args.family, args.n, args.k, seed=1)
     fam = FAM_ID[args.family]
     data = glm.GlmData(fam, x, y)
@@ -41,7 +43,7 @@ def main():
     params[:args.k], params[data.kpad], params[data.kpad + 1] = beta, alpha[0], 1.0
     dp = torch.from_numpy(params).cuda()
     dr = torch.zeros(data.result_len, dtype=torch.float64, device="cuda")
-    timers = torch.zeros(4 * 2048 + 8, dtype=torch.int64, device="cuda")
+    timers = torch.zeros(8 * 2048 + 2048 * 64, dtype=torch.int64, device="cuda")
     lib = _lib.lib()
     lib.stan_cuda_debug_set_timers.argtypes = [ctypes.c_void_p]
     lib.stan_cuda_debug_set_timers(timers.data_ptr())
@@ -61,16 +63,36 @@ def main():
         st = t[:4 * grid].reshape(grid, 4).astype(np.float64)
         end = float(t[4 * grid])
         t0 = st[:, 0].min()
-        rec = {"family": args.family, "n": args.n, "k": args.k, "threads": args.threads, "ctas": args.ctas,
+        rec = {"kernel": args.kernel, "family": args.family, "n": args.n, "k": args.k, "threads": args.threads, "ctas": args.ctas,
                "rep": rep, "grid": grid, "event_us": e0.elapsed_time(e1) * 1e3,
                "first_cta_start_to_end_us": (end - t0) / 1e3,
                "cta_start_spread_us": (st[:, 0].max() - t0) / 1e3,
                "first_tile_landed_us": {"min": (st[:, 1].min() - t0) / 1e3, "max": (st[:, 1].max() - t0) / 1e3},
                "loop_end_us": {"min": (st[:, 2].min() - t0) / 1e3, "median": (np.median(st[:, 2]) - t0) / 1e3,
                                "max": (st[:, 2].max() - t0) / 1e3},
+               "loop_end_pct_us": [round(float(v - t0) / 1e3, 1) for v in np.percentile(st[:, 2], [0, 5, 25, 50, 75, 95, 100])],
+               "loop_end_by_cta_parity_us": [round(float(np.median(st[0::2, 2]) - t0) / 1e3, 1), round(float(np.median(st[1::2, 2]) - t0) / 1e3, 1)],
+               "loop_end_first_vs_second_wave_us": [round(float(np.median(st[:148, 2]) - t0) / 1e3, 1), round(float(np.median(st[148:, 2]) - t0) / 1e3, 1)] if grid > 148 else None,
                "cta_partial_written_us": {"max": (st[:, 3].max() - t0) / 1e3},
                "final_reduce_us": (end - st[:, 3].max()) / 1e3}
-        print(json.dumps(rec), flush=True)
+        sm = t[4 * 2048 + 8:4 * 2048 + 8 + grid]
+        order = np.argsort(-st[:, 2])[:12]
+        rec["slowest_ctas"] = [[int(b), int(sm[b]), round(float(st[b, 2] - t0) / 1e3, 1)] for b in order]
+        partner = {}
+        for b in range(grid):
+            partner.setdefault(int(sm[b]), []).append(b)
+        rec["ctas_per_sm_hist"] = {str(k): v for k, v in zip(*np.unique([len(v) for v in partner.values()], return_counts=True))}
+        rec["slowest_partners"] = [[int(b), [int(q) for q in partner[int(sm[b])] if q != b]] for b in order[:6]]
+        tr = t[8 * 2048:8 * 2048 + grid * 64].reshape(grid, 2, 32).astype(np.float64)
+        def line(b, w):
+            v = tr[b, w]
+            v = v[v > 0]
+            return [round(float(q - t0) / 1e3, 1) for q in v]
+        slow_b, fast_b = int(order[0]), int(np.argsort(st[:, 2])[grid // 2])
+        rec["trace_slowest_warp0"] = line(slow_b, 0)
+        rec["trace_slowest_warp7"] = line(slow_b, 1)
+        rec["trace_median_warp0"] = line(fast_b, 0)
+        print(json.dumps(rec, default=int), flush=True)
     data.close()
 
 

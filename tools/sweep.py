@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--family", default="poisson_log")
     ap.add_argument("--n", type=int, default=2_000_000)
     ap.add_argument("--k", type=int, default=128)
+    ap.add_argument("--kernel", default="warp", choices=["warp", "cta"])
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--threads", default="128,256,512")
     ap.add_argument("--stages", default="2,3,4")
@@ -28,6 +29,7 @@ def main():
     from math_b200 import glm
     from math_b200._lib import lib
     glm.init(1)
+    lib().stan_cuda_set_kernel(1 if args.kernel == "warp" else 0)
     x, y, alpha, beta, sigma = synth_shard(args.family, args.n, args.k, seed=1)
     fam = FAM_ID[args.family]
     flags = glm.glm_flags(fam, False)
@@ -57,7 +59,7 @@ def main():
                     stream.synchronize()
                     ms = e0.elapsed_time(e1) / args.reps
                     gbs = data.algorithmic_bytes / (ms * 1e-3) / 1e9
-                    rec = {"family": args.family, "n": args.n, "k": args.k, "threads": th, "stages": st, "ctas_per_sm": ct,
+                    rec = {"kernel": args.kernel, "family": args.family, "n": args.n, "k": args.k, "threads": th, "stages": st, "ctas_per_sm": ct,
                            "ms": ms, "GBps": gbs, "frac": gbs / peak, "lp": float(dr[0])}
                 except Exception as e:  # noqa: BLE001
                     rec = {"threads": th, "stages": st, "ctas_per_sm": ct, "error": str(e)[:200]}
