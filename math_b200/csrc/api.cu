@@ -175,6 +175,14 @@ static int check_glm_args(const stan_cuda_glm_args* a) {
   return STAN_CUDA_OK;
 }
 
+static bool low_latency_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("STAN_CUDA_LOW_LATENCY");
+    return !(v && *v == '0');
+  }();
+  return on;
+}
+
 struct ShardRun {
   ThreadDev* td = nullptr;
   double *d_params = nullptr, *d_result = nullptr, *d_alpha = nullptr, *d_sigma = nullptr, *d_rowa = nullptr,
@@ -230,6 +238,13 @@ int glm_eval(const stan_cuda_glm_args* a) {
   std::vector<ShardRun> runs(S);
   const int kpad = e->shards[0].d->t.kpad;
   const size_t np = size_t(kpad) + 2, nr = size_t(kpad) + 4;
+  // Low-latency path (no per-row vectors in or out, and no separate collective behind the kernel):
+  // the parameter block travels in the kernel arguments, the kernel writes the result block and a
+  // completion flag straight into mapped pinned host memory, the host spins on the flag.  Saves the
+  // H2D copy, the D2H copy and the stream synchronisation of the general path (~15 us per call).
+  const bool per_row = alpha_vec || sigma_vec || want_rowa || want_rows;
+  const bool low_latency = !per_row && low_latency_enabled() && ((S == 1 && world == 1) || xchg != nullptr) &&
+                           np <= size_t(kInlineParams);
   for (size_t s = 0; s < S; ++s) {
     stan_cuda_data* d = e->shards[s].d;
     const int64_t rows = d->n, r0 = e->shards[s].row0;
@@ -237,7 +252,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     SC_TRY(thread_dev(d->device, &run.td));
     ThreadDev* td = run.td;
     SC_CUDA(cudaSetDevice(d->device));
-    SC_TRY(td->reserve_host(np + nr));
+    SC_TRY(td->reserve_host(np + nr + 2));
     size_t need = np + nr + 8;
     const size_t rows_al = (size_t(rows) + 1) & ~size_t(1);
     if (alpha_vec) need += rows_al;
@@ -256,7 +271,8 @@ int glm_eval(const stan_cuda_glm_args* a) {
     for (int j = 0; j < kpad; ++j) hp[j] = j < a->k ? a->beta[j] : 0.0;
     hp[kpad] = alpha_vec ? 0.0 : a->alpha[0];
     hp[kpad + 1] = (a->family == STAN_CUDA_NORMAL_ID && !sigma_vec) ? a->sigma[0] : 1.0;
-    SC_CUDA(cudaMemcpyAsync(run.d_params, hp, np * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    if (!low_latency)
+      SC_CUDA(cudaMemcpyAsync(run.d_params, hp, np * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     if (alpha_vec)
       SC_CUDA(cudaMemcpyAsync(run.d_alpha, a->alpha + r0, size_t(rows) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     if (sigma_vec)
@@ -265,6 +281,12 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (xchg) {
       io.xchg = S > 1 ? &xchg[s] : xchg;
       io.xchg_seq = xchg_seq;
+    }
+    if (low_latency) {
+      io.h_params_inline = hp;
+      io.d_result = hp + np;  // pinned + mapped: same address on the device (unified addressing)
+      io.host_flag = reinterpret_cast<unsigned long long*>(hp + np + nr);
+      io.host_seq = ++td->host_seq;
     }
     SC_TRY(launch_glm(d, io, &td->ws, td->stream));
   }
@@ -286,7 +308,28 @@ int glm_eval(const stan_cuda_glm_args* a) {
     SC_TRY(comm_allreduce_rank(runs[0].d_result, int64_t(nr), runs[0].td->stream));
   }
   // results back
-  for (size_t s = 0; s < S; ++s) {
+  if (low_latency) {
+    for (size_t s = 0; s < S; ++s) {
+      ThreadDev* td = runs[s].td;
+      volatile unsigned long long* flag = reinterpret_cast<volatile unsigned long long*>(td->h_pinned + np + nr);
+      const auto t0 = std::chrono::steady_clock::now();
+      int spins = 0;
+      while (*flag != td->host_seq) {
+        if ((++spins & 1023) == 0 &&
+            std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(250)) {
+          // long kernel (or a fault): let the driver block / report
+          SC_CUDA(cudaSetDevice(e->shards[s].d->device));
+          SC_CUDA(cudaStreamSynchronize(td->stream));
+          break;
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+      }
+      std::atomic_thread_fence(std::memory_order_acquire);
+    }
+  }
+  for (size_t s = 0; s < S && !low_latency; ++s) {
     stan_cuda_data* d = e->shards[s].d;
     const int64_t rows = d->n, r0 = e->shards[s].row0;
     ThreadDev* td = runs[s].td;
@@ -300,7 +343,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (want_rows)
       SC_CUDA(cudaMemcpyAsync(a->dsigma + r0, runs[s].d_rows, size_t(rows) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
   }
-  for (size_t s = 0; s < S; ++s) {
+  for (size_t s = 0; s < S && !low_latency; ++s) {
     SC_CUDA(cudaSetDevice(e->shards[s].d->device));
     SC_CUDA(cudaStreamSynchronize(runs[s].td->stream));
   }

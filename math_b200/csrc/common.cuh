@@ -100,7 +100,14 @@ struct LaunchIO {
   double* d_row_dsigma;       // n or null
   const struct PeerXchg* xchg = nullptr;  // non-null: all-reduce fused into the kernel (comm.cu)
   unsigned long long xchg_seq = 0;
+  // low-latency host path (api.cu): parameter block passed by value in the kernel arguments
+  // (no H2D copy) and a completion flag in mapped pinned host memory, written by the kernel after
+  // the result block (which then also lives in mapped host memory: no D2H copy, no stream sync)
+  const double* h_params_inline = nullptr;   // host pointer, params_len doubles, <= kInlineParams
+  unsigned long long* host_flag = nullptr;   // device-visible address of the flag
+  unsigned long long host_seq = 0;           // value to store
 };
+constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sigma)
 
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);

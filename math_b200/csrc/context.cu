@@ -130,7 +130,9 @@ int ThreadDev::reserve_host(size_t doubles) {
   h_pinned = nullptr;
   h_cap = 0;
   size_t cap = doubles < 1024 ? 1024 : doubles + doubles / 4;
-  SC_CUDA(cudaMallocHost(reinterpret_cast<void**>(&h_pinned), cap * sizeof(double)));
+  // mapped + portable: kernels of any device may write results into it (low-latency path, api.cu)
+  SC_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&h_pinned), cap * sizeof(double), cudaHostAllocMapped | cudaHostAllocPortable));
+  memset(h_pinned, 0, cap * sizeof(double));
   h_cap = cap;
   return STAN_CUDA_OK;
 }

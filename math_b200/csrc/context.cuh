@@ -21,6 +21,7 @@ struct ThreadDev {
   cudaStream_t stream = nullptr;
   double* h_pinned = nullptr;
   size_t h_cap = 0;  // doubles
+  unsigned long long host_seq = 0;  // completion-flag sequence of the low-latency path (api.cu)
   double* d_buf = nullptr;
   size_t d_cap = 0;  // doubles
   Workspace ws;

@@ -31,6 +31,11 @@ struct GlmKernelParams {
   double* result;
   uint32_t flags;
   double lgamma_sum;
+  // low-latency host path: parameters by value, completion flag in mapped host memory
+  int inline_n;                        // > 0: read the parameter block from inline_params
+  unsigned long long* host_flag;       // non-null: store host_seq there after the result block
+  unsigned long long host_seq;
+  double inline_params[kInlineParams];
   // all-reduce fused into the kernel (peer exchange over NVLink, comm.cu); world <= 1: off
   int xchg_world, xchg_rank;
   unsigned long long xchg_seq;
@@ -40,6 +45,10 @@ struct GlmKernelParams {
   unsigned long long* timers;  // [grid][4] globaltimer stamps: start, first tile landed, loop end, CTA partial written; [grid*4] = end of last CTA
 #endif
 };
+
+__device__ __forceinline__ double kernel_param(const GlmKernelParams& p, int i) {
+  return p.inline_n > 0 ? p.inline_params[i] : p.params[i];
+}
 
 int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, GlmKernelParams* p);
 
@@ -281,7 +290,7 @@ __device__ __forceinline__ void finish_reduction(const GlmKernelParams& p, int t
   if (tid == 0) {
     const double A0 = part[0], A1 = part[1], A2 = part[2], A3 = part[3];
     const double nn = double(p.n);
-    const double sigma0 = p.params[p.kpad + 1];
+    const double sigma0 = kernel_param(p, p.kpad + 1);
     double lp = 0.0, dsig = 0.0, witness;
     if (FAMILY == STAN_CUDA_BERNOULLI_LOGIT) {
       if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
@@ -309,6 +318,11 @@ __device__ __forceinline__ void finish_reduction(const GlmKernelParams& p, int t
   // every term of the block is additive over row shards: sum it over the devices right here
   if (p.xchg_world > 1) xchg_allreduce<NT>(p, fin, cols, tid, s_flag, sync);
   for (int c = tid; c < cols; c += NT) p.result[c] = fin[c];
+  if (p.host_flag) {  // result block is in mapped host memory: publish it
+    __threadfence_system();
+    sync();
+    if (tid == 0) st_release_sys(p.host_flag, p.host_seq);
+  }
 #ifdef STAN_CUDA_PHASE_TIMERS
   sync();
   if (tid == 0 && p.timers) p.timers[size_t(grid) * 4] = gtimer();

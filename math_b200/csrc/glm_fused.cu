@@ -91,11 +91,11 @@ glm_fused_kernel(const GlmKernelParams p) {
   double bj[kMaxKc], acc[kMaxKc];
 #pragma unroll
   for (int j = 0; j < kMaxKc; ++j) {
-    bj[j] = j < kc ? p.params[cg * kc + j] : 0.0;
+    bj[j] = j < kc ? kernel_param(p, cg * kc + j) : 0.0;
     acc[j] = 0.0;
   }
-  const double alpha0 = p.params[kpad];
-  const double sigma0 = p.params[kpad + 1];
+  const double alpha0 = kernel_param(p, kpad);
+  const double sigma0 = kernel_param(p, kpad + 1);
   const double inv_sigma0 = FAMILY == STAN_CUDA_NORMAL_ID ? 1.0 / sigma0 : 1.0;
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // owner accumulators: lp main, sum d, sum s^2, sum log sigma
 
@@ -360,6 +360,15 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->result = io.d_result;
   p->flags = io.flags;
   p->lgamma_sum = d->lgamma_sum;
+  p->inline_n = 0;
+  p->host_flag = io.host_flag;
+  p->host_seq = io.host_seq;
+  if (io.h_params_inline && t.kpad + 2 <= kInlineParams) {
+    p->inline_n = t.kpad + 2;
+    for (int i = 0; i < t.kpad + 2; ++i) p->inline_params[i] = io.h_params_inline[i];
+  } else if (!io.d_params) {
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: no parameter block");
+  }
   p->xchg_world = 0;
   p->xchg_rank = 0;
   p->xchg_seq = io.xchg_seq;

@@ -96,11 +96,11 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   double bj[kMaxKc], acc[kMaxKc];
 #pragma unroll
   for (int j = 0; j < kMaxKc; ++j) {
-    bj[j] = j < kc ? p.params[cg * kc + j] : 0.0;
+    bj[j] = j < kc ? kernel_param(p, cg * kc + j) : 0.0;
     acc[j] = 0.0;
   }
-  const double alpha0 = p.params[kpad];
-  const double sigma0 = p.params[kpad + 1];
+  const double alpha0 = kernel_param(p, kpad);
+  const double sigma0 = kernel_param(p, kpad + 1);
   const double inv_sigma0 = FAMILY == STAN_CUDA_NORMAL_ID ? 1.0 / sigma0 : 1.0;
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // lp main, sum d, sum s^2, sum log sigma (cg == 0 lanes)
   const int r_in_tile = warp * rpw + rl;
