@@ -36,6 +36,10 @@
  *                             when y is cached (the data is immutable), so the per-call O(N) host loop of
  *                             check_bounded / check_nonnegative disappears; nothing was evaluated; the C++
  *                             wrapper runs the reference's own check to throw the same std::domain_error
+ *    3  STAN_CUDA_BAD_OPERAND (normal_lpdf) an operand violates the domain the reference checks eagerly
+ *                             (y NaN, mu not finite, sigma not > 0: normal_lpdf.hpp:51-53).  The kernel
+ *                             tests every element on its way through, so the wrapper runs no O(N) check
+ *                             loops; on this code it runs the reference's checks, which throw
  *   <0  failure (bad argument, CUDA or NCCL error); stan_cuda_last_error() has the text;
  *       the C++ wrapper throws std::system_error (cf. stan/math/opencl/err/check_opencl.hpp)
  *
@@ -46,6 +50,7 @@
 #ifndef STAN_MATH_CUDA_C_API_H
 #define STAN_MATH_CUDA_C_API_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #if defined(__GNUC__)
@@ -61,6 +66,7 @@ extern "C" {
 #define STAN_CUDA_OK 0
 #define STAN_CUDA_NONFINITE 1
 #define STAN_CUDA_BAD_OUTCOME 2
+#define STAN_CUDA_BAD_OPERAND 3
 #define STAN_CUDA_ERR_ARG (-1)
 #define STAN_CUDA_ERR_CUDA (-2)
 #define STAN_CUDA_ERR_NCCL (-3)
@@ -167,6 +173,9 @@ STAN_CUDA_API void stan_cuda_set_kernel(int variant);
 /* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */
 STAN_CUDA_API int stan_cuda_glm_eval(const stan_cuda_glm_args* a);
 STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
+/* Page-locked staging memory of the calling thread (at least `bytes`, valid until the thread's next
+ * call with a larger size).  Operands gathered into it upload by DMA without a bounce buffer. */
+STAN_CUDA_API void* stan_cuda_host_staging(size_t bytes);
 
 /* ---- data cache --------------------------------------------------------------------------- */
 STAN_CUDA_API int stan_cuda_cache_invalidate(const void* host_ptr); /* drop entries keyed on this x (or y) pointer */

@@ -6,7 +6,7 @@ that identical argument blocks can be handed to the CUDA library and to the CPU 
 """
 import ctypes as C
 
-OK, NONFINITE, BAD_OUTCOME = 0, 1, 2
+OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND = 0, 1, 2, 3
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
 
 BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID = 0, 1, 2
@@ -89,6 +89,7 @@ PROTOTYPES = {
     "stan_cuda_set_kernel": (None, [C.c_int]),
     "stan_cuda_glm_eval": (C.c_int, [C.POINTER(GlmArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
+    "stan_cuda_host_staging": (C.c_void_p, [C.c_size_t]),
     "stan_cuda_cache_invalidate": (C.c_int, [C.c_void_p]),
     "stan_cuda_cache_clear": (None, []),
     "stan_cuda_cache_bytes": (C.c_int64, []),

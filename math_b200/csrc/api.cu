@@ -463,7 +463,7 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   if (need_sigma && sv) { io.dsigma_row = p; p += nal; }
   if (need_y && yv) { io.dy_row = p; p += nal; }
   SC_TRY(launch_normal_lpdf(io, &td->ws, dev, td->stream));
-  SC_CUDA(cudaMemcpyAsync(td->h_pinned, io.result, 4 * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  SC_CUDA(cudaMemcpyAsync(td->h_pinned, io.result, 5 * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
   if (io.dmu_row) SC_CUDA(cudaMemcpyAsync(a->dmu, io.dmu_row, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
   if (io.dsigma_row) SC_CUDA(cudaMemcpyAsync(a->dsigma, io.dsigma_row, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
   if (io.dy_row) SC_CUDA(cudaMemcpyAsync(a->dy, io.dy_row, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
@@ -474,7 +474,32 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   if (need_y && !yv) a->dy[0] = -res[1];
   if (need_sigma && !sv) a->dsigma[0] = res[2];
   counters().evals.fetch_add(1, std::memory_order_relaxed);
+  if (res[4] != 0.0) return STAN_CUDA_BAD_OPERAND;
   return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
+// Pinned (page-locked, portable) staging memory of the calling thread: wrappers gather the values of
+// var operands straight into it, so the upload is a full-speed DMA without a bounce buffer.
+void* host_staging(size_t bytes) {
+  struct Staging {
+    void* p = nullptr;
+    size_t cap = 0;
+  };
+  static thread_local Staging st;
+  if (bytes <= st.cap) return st.p;
+  if (ensure_init() < 0) return nullptr;
+  if (st.p) cudaFreeHost(st.p);
+  st.p = nullptr;
+  st.cap = 0;
+  const size_t cap = bytes + bytes / 4 + 4096;
+  if (cudaHostAlloc(&st.p, cap, cudaHostAllocPortable) != cudaSuccess) {
+    cudaGetLastError();
+    st.p = nullptr;
+    fail(STAN_CUDA_ERR_CUDA, "stan_cuda_host_staging: cudaHostAlloc failed");
+    return nullptr;
+  }
+  st.cap = cap;
+  return st.p;
 }
 
 }  // namespace stancuda
@@ -485,6 +510,7 @@ extern "C" {
 
 int stan_cuda_glm_eval(const stan_cuda_glm_args* a) { return glm_eval(a); }
 int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) { return normal_lpdf_eval(a); }
+void* stan_cuda_host_staging(size_t bytes) { return host_staging(bytes); }
 
 int stan_cuda_cache_invalidate(const void* host_ptr) {
   std::lock_guard<std::mutex> lk(g_cache_mu);

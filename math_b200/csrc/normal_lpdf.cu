@@ -22,6 +22,9 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
   const bool lp_const = io.flags & STAN_CUDA_LP_CONST, lp_scale = io.flags & STAN_CUDA_LP_SCALE,
              lp_main = io.flags & STAN_CUDA_LP_MAIN;
   double a_lp = 0.0, a_sd = 0.0, a_ds = 0.0;  // lp, sum scaled_diff, sum dsigma
+  // domain of the operands, checked here instead of in three O(N) host loops
+  // (check_not_nan(y), check_finite(mu), check_positive(sigma): normal_lpdf.hpp:51-53)
+  unsigned bad = 0;  // bit 0: y is NaN, bit 1: mu not finite, bit 2: sigma not > 0
   const double inv_sigma0 = 1.0 / io.sigma0, log_sigma0 = log(io.sigma0);
   for (int64_t i = blockIdx.x * int64_t(THREADS) + threadIdx.x; i < io.n; i += int64_t(gridDim.x) * THREADS) {
     const double y = io.y_vec ? io.y[i] : io.y0;
@@ -32,6 +35,8 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
       inv_sigma = 1.0 / sg;
       if (lp_scale) log_sigma = log(sg);
     }
+    bad |= (isnan(y) ? 1u : 0u) | (isfinite(mu) ? 0u : 2u);
+    if (io.sigma_vec) bad |= (io.sigma[i] > 0.0) ? 0u : 4u;
     const double z = (y - mu) * inv_sigma;           // :82-83
     const double z2 = z * z;
     double lp = 0.0;
@@ -50,6 +55,11 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
   // block reduction in fixed order
   __shared__ double sh[3][THREADS / 32];
   __shared__ int s_is_last;
+  __shared__ unsigned s_bad;
+  if (threadIdx.x == 0) s_bad = (io.sigma_vec || io.sigma0 > 0.0) ? 0u : 4u;
+  __syncthreads();
+  bad = __reduce_or_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0 && bad) atomicOr(&s_bad, bad);
   double v[3] = {a_lp, a_sd, a_ds};
 #pragma unroll
   for (int q = 0; q < 3; ++q) {
@@ -63,6 +73,7 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
     for (int w = 0; w < THREADS / 32; ++w) s += sh[threadIdx.x][w];
     p.scratch[size_t(blockIdx.x) * 4 + threadIdx.x] = s;
   }
+  if (threadIdx.x == 3) p.scratch[size_t(blockIdx.x) * 4 + 3] = double(s_bad);
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -77,6 +88,11 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
     for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.scratch + size_t(b) * 4 + threadIdx.x);
     io.result[threadIdx.x] = s;
     if (threadIdx.x == 0) io.result[3] = s;  // finiteness witness = logp
+  }
+  if (threadIdx.x == 3) {
+    unsigned all_bad = 0;
+    for (unsigned b = 0; b < gridDim.x; ++b) all_bad |= unsigned(__ldcg(p.scratch + size_t(b) * 4 + 3));
+    io.result[4] = double(all_bad);
   }
   __syncthreads();
   if (threadIdx.x == 0) *p.ticket = 0u;

@@ -242,7 +242,9 @@ def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
     a.y, a.y_len, a.mu, a.mu_len = y.ctypes.data, y.size, mu.ctypes.data, mu.size
     a.sigma, a.sigma_len = sigma.ctypes.data, sigma.size
     a.lp, a.dmu, a.dsigma, a.dy = lp.ctypes.data, dmu.ctypes.data, dsigma.ctypes.data, dy.ctypes.data
-    check(lib().stan_cuda_normal_lpdf_eval(C.byref(a)))
+    rc = check(lib().stan_cuda_normal_lpdf_eval(C.byref(a)))
+    if rc == _abi.BAD_OPERAND:   # unreachable after the checks above; kept for symmetry with the C++ wrapper
+        raise DomainError("%s: operand outside the domain" % function)
     grads = {"mu": dmu, "sigma": dsigma}
     if need_dy:
         grads["y"] = dy

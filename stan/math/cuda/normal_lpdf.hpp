@@ -10,6 +10,12 @@
 #include <stan/math/prim/scal/err/check_not_nan.hpp>
 #include <stan/math/prim/scal/err/check_positive.hpp>
 #include <stan/math/prim/scal/fun/size_zero.hpp>
+#ifdef STAN_THREADS
+#include <tbb/blocked_range.h>
+#include <tbb/parallel_for.h>
+#endif
+#include <stdexcept>
+#include <string>
 
 namespace stan {
 namespace math {
@@ -24,10 +30,55 @@ struct normal_lpdf_eligible
                                            || is_vector<T_scale>::value)> {};
 
 /**
+ * Values of one operand as contiguous doubles for the device.  Double containers are borrowed;
+ * var / int containers are gathered -- one pass, in parallel over TBB workers when STAN_THREADS is
+ * on -- straight into the thread's page-locked staging area (stan_cuda_host_staging), so the
+ * upload is a DMA without a bounce buffer.  No domain checks here: the kernel tests every element.
+ */
+template <typename T>
+struct staged_operand {
+  static constexpr bool borrowed = false;
+  static size_t bytes(const T& v) { return ((length(v) + 1) & ~size_t(1)) * sizeof(double); }
+  static const double* fill(const T& v, double* dst) {
+    scalar_seq_view<T> view(v);
+    const size_t n = length(v);
+#ifdef STAN_THREADS
+    if (n >= (size_t(1) << 16)) {
+      tbb::parallel_for(tbb::blocked_range<size_t>(0, n, size_t(1) << 15),
+                        [&](const tbb::blocked_range<size_t>& r) {
+                          for (size_t i = r.begin(); i != r.end(); ++i) {
+                            dst[i] = value_of_rec(view[i]);
+                          }
+                        });
+      return dst;
+    }
+#endif
+    for (size_t i = 0; i < n; ++i) {
+      dst[i] = value_of_rec(view[i]);
+    }
+    return dst;
+  }
+};
+template <>
+struct staged_operand<std::vector<double>> {
+  static constexpr bool borrowed = true;
+  static size_t bytes(const std::vector<double>&) { return 0; }
+  static const double* fill(const std::vector<double>& v, double*) { return v.data(); }
+};
+template <int R, int C, int O, int MR, int MC>
+struct staged_operand<Eigen::Matrix<double, R, C, O, MR, MC>> {
+  static constexpr bool borrowed = true;
+  static size_t bytes(const Eigen::Matrix<double, R, C, O, MR, MC>&) { return 0; }
+  static const double* fill(const Eigen::Matrix<double, R, C, O, MR, MC>& v, double*) { return v.data(); }
+};
+
+/**
  * GPU body of the vectorised normal_lpdf (reference: stan/math/prim/scal/prob/normal_lpdf.hpp).
- * Checks :45-58 unchanged and eager; the loop :78-110 becomes one kernel that returns the
- * log-density and the partials of every non-constant operand (per element for containers, summed
- * for scalars -- what the reference accumulates through broadcast_array).
+ * The loop :78-110 becomes one kernel that returns the log-density and the partials of every
+ * non-constant operand (per element for containers, summed for scalars -- what the reference
+ * accumulates through broadcast_array).  The eager domain checks :51-53 are answered by the same
+ * kernel (STAN_CUDA_BAD_OPERAND); the reference's check functions then run on the host only to
+ * throw the identical exception.  Size checks :54-55 stay in front.
  */
 template <bool propto, typename T_y, typename T_loc, typename T_scale>
 return_type_t<T_y, T_loc, T_scale> normal_lpdf_device(const T_y& y, const T_loc& mu, const T_scale& sigma) {
@@ -35,28 +86,44 @@ return_type_t<T_y, T_loc, T_scale> normal_lpdf_device(const T_y& y, const T_loc&
   if (size_zero(y, mu, sigma)) {
     return 0.0;
   }
-  check_not_nan(function, "Random variable", y);
-  check_finite(function, "Location parameter", mu);
-  check_positive(function, "Scale parameter", sigma);
-  check_consistent_sizes(function, "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
-  if (!include_summand<propto, T_y, T_loc, T_scale>::value) {
+  if (!include_summand<propto, T_y, T_loc, T_scale>::value) {  // nothing goes to the device
+    check_not_nan(function, "Random variable", y);
+    check_finite(function, "Location parameter", mu);
+    check_positive(function, "Scale parameter", sigma);
+    check_consistent_sizes(function, "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
     return 0.0;
+  }
+  // the reference reports a domain error before a size error (:51-55): if the sizes disagree,
+  // run its checks in its order and let the first one throw
+  const size_t N = max_size(y, mu, sigma);
+  if ((is_vector<T_y>::value && length(y) != N) || (is_vector<T_loc>::value && length(mu) != N)
+      || (is_vector<T_scale>::value && length(sigma) != N)) {
+    check_not_nan(function, "Random variable", y);
+    check_finite(function, "Location parameter", mu);
+    check_positive(function, "Scale parameter", sigma);
+    check_consistent_sizes(function, "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
   }
 
   operands_and_partials<T_y, T_loc, T_scale> ops_partials(y, mu, sigma);
-  values<T_y> y_val(y);
-  values<T_loc> mu_val(mu);
-  values<T_scale> sigma_val(sigma);
+  const size_t by = staged_operand<T_y>::bytes(y), bm = staged_operand<T_loc>::bytes(mu),
+               bs = staged_operand<T_scale>::bytes(sigma);
+  double* stage = nullptr;
+  if (by + bm + bs > 0) {
+    stage = static_cast<double*>(stan_cuda_host_staging(by + bm + bs));
+    if (!stage) {
+      check_cuda_rc(function, STAN_CUDA_ERR_CUDA);
+    }
+  }
   double logp = 0;
   stan_cuda_normal_args a = stan_cuda_normal_args();
-  a.n = max_size(y, mu, sigma);
-  a.y = y_val.data();
-  a.y_len = y_val.size();
-  a.y_is_data = (is_constant_all<T_y>::value && y_val.borrowed()) ? 1 : 0;
-  a.mu = mu_val.data();
-  a.mu_len = mu_val.size();
-  a.sigma = sigma_val.data();
-  a.sigma_len = sigma_val.size();
+  a.n = N;
+  a.y = staged_operand<T_y>::fill(y, stage);
+  a.y_len = length(y);
+  a.y_is_data = (is_constant_all<T_y>::value && staged_operand<T_y>::borrowed) ? 1 : 0;
+  a.mu = staged_operand<T_loc>::fill(mu, stage + by / sizeof(double));
+  a.mu_len = length(mu);
+  a.sigma = staged_operand<T_scale>::fill(sigma, stage + (by + bm) / sizeof(double));
+  a.sigma_len = length(sigma);
   a.lp = &logp;
   a.flags = STAN_CUDA_LP_MAIN;
   if (include_summand<propto>::value) {
@@ -77,7 +144,14 @@ return_type_t<T_y, T_loc, T_scale> normal_lpdf_device(const T_y& y, const T_loc&
     a.flags |= STAN_CUDA_NEED_DSIGMA;
     a.dsigma = partials_data(ops_partials.edge3_);
   }
-  check_cuda_rc(function, stan_cuda_normal_lpdf_eval(&a));
+  const int rc = stan_cuda_normal_lpdf_eval(&a);
+  check_cuda_rc(function, rc);
+  if (rc == STAN_CUDA_BAD_OPERAND) {
+    check_not_nan(function, "Random variable", y);
+    check_finite(function, "Location parameter", mu);
+    check_positive(function, "Scale parameter", sigma);
+    throw std::domain_error(std::string(function) + ": operand outside the domain (device check)");
+  }
   return ops_partials.build(logp);
 }
 

@@ -262,6 +262,43 @@ TEST(CudaNormalLpdf, vectorised_matches_reference_loop) {
   stan::math::recover_memory();
 }
 
+TEST(CudaNormalLpdf, same_exceptions_as_the_reference) {
+  using stan::math::normal_lpdf;
+  const int n = 1000;
+  VectorXd y = VectorXd::LinSpaced(n, -1, 1), mu_d = VectorXd::Constant(n, 0.1);
+  vector_v mu = to_v(mu_d);
+  var sigma = 1.5;
+  VectorXd y_nan = y;
+  y_nan[777] = NAN;
+  EXPECT_THROW(normal_lpdf(y_nan, mu, sigma), std::domain_error);
+  vector_v mu_inf = to_v(mu_d);
+  mu_inf[3] = INFINITY;
+  EXPECT_THROW(normal_lpdf(y, mu_inf, sigma), std::domain_error);
+  var sigma0 = 0.0, sigma_neg = -1.0;
+  EXPECT_THROW(normal_lpdf(y, mu, sigma0), std::domain_error);
+  EXPECT_THROW(normal_lpdf(y, mu, sigma_neg), std::domain_error);
+  vector_v sigma_v = to_v(VectorXd::Constant(n, 2.0));
+  sigma_v[999] = -2.0;
+  EXPECT_THROW(normal_lpdf(y, mu, sigma_v), std::domain_error);
+  vector_v mu_short = to_v(VectorXd::Constant(n - 1, 0.1));
+  EXPECT_THROW(normal_lpdf(y, mu_short, sigma), std::invalid_argument);
+  // same message as the reference loop
+  std::string m_gpu, m_cpu;
+  try {
+    normal_lpdf(y_nan, mu, sigma);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    stan::math::normal_lpdf_reference_cpu<false>(y_nan, mu, sigma);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  stan::math::recover_memory();
+}
+
 // --- map_rect: shards dispatched to devices ------------------------------------------------------
 struct glm_shard {
   template <typename T1, typename T2>
