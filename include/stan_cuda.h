@@ -15,6 +15,7 @@
  *                                  stan/math/opencl/prim/{bernoulli_logit,poisson_log,normal_id}_glm_*.hpp
  *                                  stan/math/opencl/kernels/{bernoulli_logit,poisson_log,normal_id}_glm_*.hpp
  *                                  stan/math/opencl/kernels/matrix_multiply.hpp:354-386 (row_vector_matrix_multiply)
+ *                                  neg_binomial_2_log_glm_lpmf stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:108-197
  *   stan_cuda_normal_lpdf_eval   the loop of normal_lpdf      stan/math/prim/scal/prob/normal_lpdf.hpp:67-110
  *   stan_cuda_data_* / cache_*   matrix_cl + to_matrix_cl      stan/math/opencl/matrix_cl.hpp:32-454, stan/math/opencl/copy.hpp:37-93
  *                                and the cache-by-call_id of the MPI backend
@@ -76,6 +77,7 @@ extern "C" {
 #define STAN_CUDA_BERNOULLI_LOGIT 0
 #define STAN_CUDA_POISSON_LOG 1
 #define STAN_CUDA_NORMAL_ID 2
+#define STAN_CUDA_NEG_BINOMIAL_2_LOG 3 /* precision phi travels in the sigma slot, d/dphi in dsigma */
 
 /* flags: which summands of the log-density to include (the reference decides this at compile
  * time with include_summand<propto, ...>, stan/math/prim/scal/meta/include_summand.hpp) and
@@ -84,6 +86,10 @@ extern "C" {
 #define STAN_CUDA_LP_SCALE 0x02u   /* -sum log(sigma)  (normal_id_glm, normal_lpdf)                */
 #define STAN_CUDA_LP_MAIN 0x04u    /* the parameter-dependent part                                */
 #define STAN_CUDA_LP_ALL 0x07u
+/* neg_binomial_2_log only: the sum(y * theta) term, which the reference ties to
+ * include_summand<propto, T_x, T_alpha, T_beta> (neg_binomial_2_log_glm_lpmf.hpp:148-150) while
+ * LP_MAIN is the -sum((y + phi) * logsumexp(theta, log phi)) term (:145-147) */
+#define STAN_CUDA_LP_LINEAR 0x200u
 #define STAN_CUDA_NEED_DBETA 0x08u
 #define STAN_CUDA_NEED_DALPHA 0x10u /* GLM: d/dalpha ; normal_lpdf: d/dmu                          */
 #define STAN_CUDA_NEED_DSIGMA 0x20u
@@ -95,7 +101,7 @@ extern "C" {
 #define STAN_CUDA_FUSED_ALLREDUCE 0x100u
 
 typedef struct stan_cuda_glm_args {
-  int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID */
+  int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID | NEG_BINOMIAL_2_LOG */
   uint32_t flags;      /* STAN_CUDA_LP_* | STAN_CUDA_NEED_* */
   int64_t n;           /* rows of x (instances) */
   int64_t k;           /* columns of x (attributes) */
@@ -107,8 +113,8 @@ typedef struct stan_cuda_glm_args {
   const double* alpha; /* host; alpha_len doubles */
   int64_t alpha_len;   /* 1 (scalar intercept) or n */
   const double* beta;  /* host; k doubles */
-  const double* sigma; /* host; normal_id only */
-  int64_t sigma_len;   /* 0 (not normal_id), 1 or n */
+  const double* sigma; /* host; normal_id: scale sigma; neg_binomial_2_log: precision phi */
+  int64_t sigma_len;   /* 0 (bernoulli, poisson), 1 or n */
   /* outputs: host memory owned by the caller, NULL when the matching NEED_ flag is off */
   double* lp;          /* [1] */
   double* dbeta;       /* [k] */

@@ -9,10 +9,13 @@ import ctypes as C
 OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND = 0, 1, 2, 3
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
 
-BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID = 0, 1, 2
-FAMILIES = {"bernoulli_logit": BERNOULLI_LOGIT, "poisson_log": POISSON_LOG, "normal_id": NORMAL_ID}
+BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID, NEG_BINOMIAL_2_LOG = 0, 1, 2, 3
+FAMILIES = {"bernoulli_logit": BERNOULLI_LOGIT, "poisson_log": POISSON_LOG, "normal_id": NORMAL_ID,
+            "neg_binomial_2_log": NEG_BINOMIAL_2_LOG}
+HAS_SCALE = (NORMAL_ID, NEG_BINOMIAL_2_LOG)   # families with a fifth operand (sigma | phi)
 
 LP_CONST, LP_SCALE, LP_MAIN, LP_ALL = 0x01, 0x02, 0x04, 0x07
+LP_LINEAR = 0x200
 NEED_DBETA, NEED_DALPHA, NEED_DSIGMA, NEED_DY, NEED_ALL = 0x08, 0x10, 0x20, 0x40, 0x78
 FUSED_ALLREDUCE = 0x100
 

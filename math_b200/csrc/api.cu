@@ -155,20 +155,27 @@ static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* ou
   return STAN_CUDA_OK;
 }
 
+// families with a fifth operand in the sigma slot (normal_id: sigma, neg_binomial_2_log: phi)
+static inline bool has_scale(int family) {
+  return family == STAN_CUDA_NORMAL_ID || family == STAN_CUDA_NEG_BINOMIAL_2_LOG;
+}
+
 static int check_glm_args(const stan_cuda_glm_args* a) {
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null args");
-  if (a->family < 0 || a->family > 2) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: unknown family");
+  if (a->family < 0 || a->family > 3) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: unknown family");
   if (a->n < 0 || a->k < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: negative size");
   if (a->n > 0 && (!a->y || (!a->x && a->k > 0))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null x or y");
   if (a->k > 0 && !a->beta) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null beta");
   if (!a->alpha || (a->alpha_len != 1 && a->alpha_len != a->n))
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: alpha_len must be 1 or n");
-  if (a->family == STAN_CUDA_NORMAL_ID) {
+  if (has_scale(a->family)) {
     if (!a->sigma || (a->sigma_len != 1 && a->sigma_len != a->n))
       return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: sigma_len must be 1 or n");
+  }
+  if (a->family == STAN_CUDA_NORMAL_ID) {
     if (!a->y_is_double) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: normal_id needs double y");
   } else if (a->y_is_double) {
-    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: bernoulli/poisson need int32 y");
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: bernoulli/poisson/neg_binomial need int32 y");
   }
   if (a->k > 0 && a->ldx < (a->x_row_major ? a->k : a->n))
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: ldx too small");
@@ -211,7 +218,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (lo < 0 || (a->family == STAN_CUDA_BERNOULLI_LOGIT && hi > 1)) return STAN_CUDA_BAD_OUTCOME;
   }
   const bool alpha_vec = a->alpha_len != 1;
-  const bool sigma_vec = a->family == STAN_CUDA_NORMAL_ID && a->sigma_len != 1;
+  const bool sigma_vec = has_scale(a->family) && a->sigma_len != 1;
   const bool want_rowa = ((a->flags & STAN_CUDA_NEED_DALPHA) && alpha_vec && a->dalpha) ||
                          ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID);
   const bool want_rows = (a->flags & STAN_CUDA_NEED_DSIGMA) && sigma_vec && a->dsigma;
@@ -270,7 +277,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     double* hp = td->h_pinned;
     for (int j = 0; j < kpad; ++j) hp[j] = j < a->k ? a->beta[j] : 0.0;
     hp[kpad] = alpha_vec ? 0.0 : a->alpha[0];
-    hp[kpad + 1] = (a->family == STAN_CUDA_NORMAL_ID && !sigma_vec) ? a->sigma[0] : 1.0;
+    hp[kpad + 1] = (has_scale(a->family) && !sigma_vec) ? a->sigma[0] : 1.0;
     if (!low_latency)
       SC_CUDA(cudaMemcpyAsync(run.d_params, hp, np * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     if (alpha_vec)
@@ -351,7 +358,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
   if (a->lp) *a->lp = res[0];
   if ((a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) memcpy(a->dbeta, res + 4, size_t(a->k) * sizeof(double));
   if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha && !alpha_vec) a->dalpha[0] = res[1];
-  if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma && a->family == STAN_CUDA_NORMAL_ID && !sigma_vec)
+  if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma && has_scale(a->family) && !sigma_vec)
     a->dsigma[0] = res[2];
   if ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID) {
     // dy = -mu_derivative (normal_id_glm_lpdf.hpp:118-120); the kernel wrote mu_derivative

@@ -58,7 +58,7 @@ struct Tiling {
 };
 
 // Picks C, kc, R for k columns and n rows; returns false if k is outside the fused kernel's range.
-bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t);
+bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t, int force_layout = -1);
 
 struct Workspace {   // per (host thread, device) or per data handle: one launch in flight at a time
   int device = -1;
@@ -82,6 +82,8 @@ struct stan_cuda_data {
   void* y = nullptr;     // int32 or double, padded to tiles * R
   double lgamma_sum = 0; // sum lgamma(y+1) (poisson), computed once at fill
   int64_t y_min = 0, y_max = 0;  // range of the integer outcomes, computed once at fill
+  unsigned int* hist = nullptr;  // neg_binomial_2_log: histogram of y (counts of 0 .. y_max), built at fill
+  int hist_len = 0;
   size_t bytes = 0;
   stancuda::Workspace ws;  // used by the device-level API (stan_cuda_glm_launch)
 };

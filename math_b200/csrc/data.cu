@@ -67,6 +67,12 @@ __global__ void retile_rowmajor_kernel(const double* __restrict__ src, int64_t s
 //                  O(N) host loop;
 //   sum lgamma(y + 1) (poisson_log_glm_lpmf.hpp:102-108), depends on data only.
 // Per-block partials in block order, combined on the host in order.
+// Histogram of the integer outcomes (neg_binomial_2_log; integer atomics: exact, order-free).
+__global__ void y_hist_kernel(const int* __restrict__ y, int64_t n, unsigned int* __restrict__ hist) {
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
+    atomicAdd(&hist[y[i]], 1u);
+}
+
 __global__ void y_stats_kernel(const int* __restrict__ y, int64_t n, int want_lgamma, double* __restrict__ partial,
                                int* __restrict__ minmax) {
   __shared__ double sh[256];
@@ -199,8 +205,8 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
     double* partial = nullptr;  // [nb] doubles followed by [2 * nb] ints
     SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&partial), nb * (sizeof(double) + 2 * sizeof(int))));
     int* mm = reinterpret_cast<int*>(partial + nb);
-    y_stats_kernel<<<nb, 256, 0, stream>>>(static_cast<const int*>(d->y), n, d->family == STAN_CUDA_POISSON_LOG,
-                                           partial, mm);
+    const int want_lgamma = d->family == STAN_CUDA_POISSON_LOG || d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG;
+    y_stats_kernel<<<nb, 256, 0, stream>>>(static_cast<const int*>(d->y), n, want_lgamma, partial, mm);
     double host[256];
     int hmm[512];
     cudaError_t e = cudaMemcpyAsync(host, partial, sizeof(host), cudaMemcpyDeviceToHost, stream);
@@ -219,6 +225,16 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
     d->y_min = lo;
     d->y_max = hi;
     counters().launches.fetch_add(1, std::memory_order_relaxed);
+    // neg_binomial_2_log: histogram of y, so that sum lgamma(y + phi) and sum digamma(y + phi) cost
+    // O(y_max) per evaluation instead of O(N) special-function calls in the hot loop
+    if (d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG && lo >= 0 && hi < (1 << 20)) {
+      d->hist_len = hi + 1;
+      SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&d->hist), size_t(d->hist_len) * sizeof(unsigned int)));
+      SC_CUDA_CLEAN(cudaMemsetAsync(d->hist, 0, size_t(d->hist_len) * sizeof(unsigned int), stream));
+      y_hist_kernel<<<sm_count(d->device) * 4, 256, 0, stream>>>(static_cast<const int*>(d->y), n, d->hist);
+      SC_CUDA_CLEAN(cudaGetLastError());
+      d->bytes += size_t(d->hist_len) * sizeof(unsigned int);
+    }
   }
   SC_CUDA_CLEAN(cudaStreamSynchronize(stream));
 #undef SC_CUDA_CLEAN
@@ -231,14 +247,15 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
                     int x_row_major, const void* y, int y_is_double, int64_t row0, cudaStream_t stream,
                     stan_cuda_data** out) {
   if (n_rows <= 0 || k < 0 || (!x && k > 0) || !y) return fail(STAN_CUDA_ERR_ARG, "data block: bad shape or null pointer");
-  if (family < 0 || family > 2) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
+  if (family < 0 || family > 3) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
   stan_cuda_data* d = new stan_cuda_data();
   d->device = device;
   d->family = family;
   d->n = n_rows;
   d->k = k;
   d->y_is_double = y_is_double;
-  if (!choose_tiling(n_rows, k, 0, &d->t)) {
+  // neg_binomial_2_log exists on the warp kernel only
+  if (!choose_tiling(n_rows, k, 0, &d->t, family == STAN_CUDA_NEG_BINOMIAL_2_LOG ? kLayoutWarp : -1)) {
     delete d;
     return fail(STAN_CUDA_ERR_ARG, "data block: k > 512 is outside the fused kernel's range");
   }
@@ -248,6 +265,7 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
   if (rc < 0) {
     if (d->x) cudaFree(d->x);
     if (d->y) cudaFree(d->y);
+    if (d->hist) cudaFree(d->hist);
     delete d;
     return rc;
   }
@@ -263,6 +281,7 @@ void free_data_block(stan_cuda_data* d) {
   cudaSetDevice(d->device);
   if (d->x) cudaFree(d->x);
   if (d->y) cudaFree(d->y);
+  if (d->hist) cudaFree(d->hist);
   workspace_free(&d->ws);
   delete d;
 }

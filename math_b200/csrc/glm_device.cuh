@@ -31,6 +31,8 @@ struct GlmKernelParams {
   double* result;
   uint32_t flags;
   double lgamma_sum;
+  const double* nb_sums;  // neg_binomial_2_log with a histogram of y: [sum lgamma(y+phi), sum digamma(y+phi)]
+  int nb_rowfun;          // neg_binomial_2_log: per-row lgamma/digamma (vector phi or no histogram)
   // low-latency host path: parameters by value, completion flag in mapped host memory
   int inline_n;                        // > 0: read the parameter block from inline_params
   unsigned long long* host_flag;       // non-null: store host_seq there after the result block
@@ -191,8 +193,52 @@ __device__ __forceinline__ void xchg_allreduce(const GlmKernelParams& p, double*
 struct RowTerms {
   double d;   // derivative wrt the linear predictor
   double t0;  // -> lp main term
-  double t2;  // normal: s^2
+  double t2;  // normal: s^2; neg_binomial_2_log: theta (finiteness witness)
+  double t3;  // neg_binomial_2_log: per-row part of d/dphi
 };
+
+// digamma for x > 0: recurrence up to x >= 10, then the asymptotic series
+// ln x - 1/(2x) - sum B_2k / (2k x^2k) with 7 terms (error < 1e-17 at x = 10).  The reference calls
+// boost::math::digamma (stan/math/prim/scal/fun/digamma.hpp); agreement is pinned in the tests.
+__device__ __forceinline__ double digamma_pos(double x) {
+  double r = 0.0;
+  while (x < 10.0) {
+    r -= 1.0 / x;
+    x += 1.0;
+  }
+  const double f = 1.0 / (x * x);
+  const double t = f * (-1.0 / 12.0 + f * (1.0 / 120.0 + f * (-1.0 / 252.0 + f * (1.0 / 240.0 +
+                   f * (-1.0 / 132.0 + f * (691.0 / 32760.0 + f * (-1.0 / 12.0)))))));
+  return r + log(x) - 0.5 / x + t;
+}
+
+// neg_binomial_2_log_glm_lpmf.hpp:118-190, one row.  `rowfun`: lgamma / digamma of (y + phi) and
+// phi are evaluated per row (vector phi, or no histogram of y); otherwise the caller adds their
+// sums from the histogram of y (nb_hist_sums_kernel).  t0 is the row's contribution to the
+// log-density under `flags`; t3 the row's contribution to d/dphi.
+__device__ __forceinline__ RowTerms nb_row_epilogue(double eta, double alpha, double yv, double phi,
+                                                    double log_phi, uint32_t flags, bool rowfun) {
+  RowTerms o;
+  const double theta = eta + alpha;                                           // :118-119
+  const double lse = theta > log_phi ? theta + log1p(exp(log_phi - theta))    // :122-125
+                                     : log_phi + log1p(exp(theta - log_phi));
+  const double ypp = yv + phi;                                                // :127
+  const double te = exp(theta);                                               // :159
+  const double q = ypp / (te + phi);
+  o.d = yv - te * q;                                                          // :162
+  double lp = 0.0;
+  if (flags & STAN_CUDA_LP_MAIN) lp -= ypp * lse;                             // :145-147
+  if (flags & STAN_CUDA_LP_LINEAR) lp += yv * theta;                          // :148-150
+  double t3 = -q + log_phi - lse;                                             // :185-190
+  if (rowfun) {
+    if (flags & STAN_CUDA_LP_SCALE) lp += phi * log_phi - lgamma(phi) + lgamma(ypp);  // :137, :152
+    if (flags & STAN_CUDA_NEED_DSIGMA) t3 += digamma_pos(ypp) - digamma_pos(phi);
+  }
+  o.t0 = lp;
+  o.t2 = theta;
+  o.t3 = t3;
+  return o;
+}
 
 template <int FAMILY>
 __device__ __forceinline__ RowTerms row_epilogue(double eta, double alpha, double yv, double inv_sigma) {
@@ -219,6 +265,7 @@ __device__ __forceinline__ RowTerms row_epilogue(double eta, double alpha, doubl
     o.t2 = s * s;
     o.t0 = 0.0;
   }
+  o.t3 = 0.0;
   return o;
 }
 
@@ -299,6 +346,18 @@ __device__ __forceinline__ void finish_reduction(const GlmKernelParams& p, int t
       if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;  // :102-108
       if (p.flags & STAN_CUDA_LP_MAIN) lp += A0;             // :109-112
       witness = A1;  // poisson_log_glm_lpmf.hpp:97 tests sum(theta_derivative)
+    } else if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
+      // neg_binomial_2_log_glm_lpmf.hpp:130-153, :185-190; A0 already holds the flagged row terms
+      const double phi = sigma0;
+      lp = A0;
+      if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;
+      if (!p.nb_rowfun) {
+        if (p.flags & STAN_CUDA_LP_SCALE) lp += nn * (phi * log(phi) - lgamma(phi)) + p.nb_sums[0];
+        dsig = nn + A3 + p.nb_sums[1] - nn * digamma_pos(phi);
+      } else if (!p.sigma_vec) {
+        dsig = nn + A3;
+      }
+      witness = A2;  // :120 check_finite(theta)
     } else {
       // normal_id_glm_lpdf.hpp:159-172
       const double NEG_LOG_SQRT_TWO_PI = -0.91893853320467274178032973640561763986;

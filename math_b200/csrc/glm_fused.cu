@@ -253,9 +253,10 @@ int sm_count(int device) {
   return cached[device];
 }
 
-bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t) {
+bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t, int force_layout) {
   if (k < 1) k = 1;
-  if (tuning().layout == kLayoutWarp) {
+  const int layout = force_layout >= 0 ? force_layout : tuning().layout;
+  if (layout == kLayoutWarp) {
     // 8 consumer warps of 32 lanes; smallest power-of-two C <= 32 with at most kMaxKc columns per lane
     int C = 1;
     while ((k + C - 1) / C > kMaxKc) C *= 2;
@@ -341,6 +342,8 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->group_size = 1;
   p->stage_bytes = 0;
   p->blocked = 0;
+  p->nb_sums = nullptr;
+  p->nb_rowfun = 1;
   p->x = d->x;
   p->y = d->y;
   p->n = d->n;
@@ -390,6 +393,8 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
   if (t.layout == kLayoutWarp) return launch_glm_warp(d, io, ws, stream);
+  if (d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG)
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: neg_binomial_2_log runs on the warp kernel only");
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
   const int sms = sm_count(d->device);
   int ctas_per_sm = tuning().ctas_per_sm;

@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   const double alpha0 = kernel_param(p, kpad);
   const double sigma0 = kernel_param(p, kpad + 1);
   const double inv_sigma0 = FAMILY == STAN_CUDA_NORMAL_ID ? 1.0 / sigma0 : 1.0;
+  const double log_sigma0 = FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG ? log(sigma0) : 0.0;  // log phi
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // lp main, sum d, sum s^2, sum log sigma (cg == 0 lanes)
   const int r_in_tile = warp * rpw + rl;
 
@@ -121,7 +122,7 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
 #pragma unroll
     for (int j = 0; j < kMaxKc; ++j) xr[j] = j < kc ? xs[j * NT] : 0.0;
     double yv;
-    if (FAMILY == STAN_CUDA_NORMAL_ID) {
+    if (FAMILY == STAN_CUDA_NORMAL_ID) {  // the only family with real-valued outcomes
       yv = reinterpret_cast<const double*>(st + p.tile_bytes)[r_in_tile];
     } else {
       yv = double(reinterpret_cast<const int*>(st + p.tile_bytes)[r_in_tile]);
@@ -148,26 +149,35 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
     // partial dots of the C column groups of a row: xor butterfly, identical result in every lane
     for (int off = 1; off < C; off <<= 1) eta += __shfl_xor_sync(0xffffffffu, eta, off);
 
-    double alpha = alpha0, inv_sigma = inv_sigma0, sigma_row = sigma0;
+    double alpha = alpha0, inv_sigma = inv_sigma0, sigma_row = sigma0, log_sigma_row = log_sigma0;
     const bool valid = row < p.n;
     if (ROWIO && valid) {
       if (p.alpha_vec) alpha = p.alpha_vec[row];
-      if (FAMILY == STAN_CUDA_NORMAL_ID && p.sigma_vec) {
+      if (FAMILY >= STAN_CUDA_NORMAL_ID && p.sigma_vec) {
         sigma_row = p.sigma_vec[row];
-        inv_sigma = 1.0 / sigma_row;
+        if (FAMILY == STAN_CUDA_NORMAL_ID) inv_sigma = 1.0 / sigma_row;
+        else log_sigma_row = log(sigma_row);
       }
     }
-    const RowTerms o = row_epilogue<FAMILY>(eta, alpha, yv, inv_sigma);
+    RowTerms o;
+    if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
+      o = nb_row_epilogue(eta, alpha, yv, sigma_row, log_sigma_row, p.flags, p.nb_rowfun != 0);
+    } else {
+      o = row_epilogue<FAMILY>(eta, alpha, yv, inv_sigma);
+    }
     const double d = valid ? o.d : 0.0;
     if (valid && cg == 0) {
       a0 += o.t0;
       a1 += o.d;
       a2 += o.t2;
+      if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) a3 += o.t3;
       if (ROWIO) {
         if (FAMILY == STAN_CUDA_NORMAL_ID && p.sigma_vec) {
           a3 += log(sigma_row);
           if (p.row_dsigma) p.row_dsigma[row] = (o.t2 - 1.0) * inv_sigma;
         }
+        if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG && p.sigma_vec && p.row_dsigma)
+          p.row_dsigma[row] = 1.0 + o.t3;                                     // :180-183
         if (p.row_dalpha) p.row_dalpha[row] = o.d;
       }
     }
@@ -246,6 +256,55 @@ static int launch_warp_inst(const GlmKernelParams& p, int grid, size_t smem, cud
   return STAN_CUDA_OK;
 }
 
+// neg_binomial_2_log with a scalar phi: sum_i lgamma(y_i + phi) and sum_i digamma(y_i + phi) depend on
+// the data only through the histogram of y, which is built once at cache fill.  One small CTA turns
+// the histogram into the two sums per evaluation (O(y_max) special-function calls instead of O(N)
+// inside the hot loop); fixed-order tree reduction, so the sums are bit-reproducible.
+__global__ void __launch_bounds__(256) nb_hist_sums_kernel(const unsigned int* __restrict__ hist, int len,
+                                                           const double* d_params, int phi_index, double phi_inline,
+                                                           int use_inline, double* __restrict__ out) {
+  __shared__ double sh[2][256];
+  const double phi = use_inline ? phi_inline : d_params[phi_index];
+  double s_lg = 0.0, s_dg = 0.0;
+  for (int v = threadIdx.x; v < len; v += 256) {
+    const unsigned int c = hist[v];
+    if (c) {
+      s_lg += double(c) * lgamma(double(v) + phi);
+      s_dg += double(c) * digamma_pos(double(v) + phi);
+    }
+  }
+  sh[0][threadIdx.x] = s_lg;
+  sh[1][threadIdx.x] = s_dg;
+  __syncthreads();
+  for (int off = 128; off > 0; off >>= 1) {
+    if (int(threadIdx.x) < off) {
+      sh[0][threadIdx.x] += sh[0][threadIdx.x + off];
+      sh[1][threadIdx.x] += sh[1][threadIdx.x + off];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    out[0] = sh[0][0];
+    out[1] = sh[1][0];
+  }
+}
+
+static int prepare_neg_binomial(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, GlmKernelParams* p,
+                                cudaStream_t stream) {
+  p->nb_sums = nullptr;
+  p->nb_rowfun = 1;
+  if (io.d_sigma_vec || !d->hist) return STAN_CUDA_OK;  // vector phi, or outcomes too large for a histogram
+  double* out = ws->scratch + ws->scratch_doubles - 2;  // last two doubles of the workspace
+  const bool inl = p->inline_n > 0;
+  nb_hist_sums_kernel<<<1, 256, 0, stream>>>(d->hist, d->hist_len, io.d_params, d->t.kpad + 1,
+                                             inl ? p->inline_params[d->t.kpad + 1] : 0.0, inl ? 1 : 0, out);
+  SC_CUDA(cudaGetLastError());
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
+  p->nb_sums = out;
+  p->nb_rowfun = 0;
+  return STAN_CUDA_OK;
+}
+
 int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
@@ -270,7 +329,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   while (group_size * group_size < grid) ++group_size;
   const int ngroups = (grid + group_size - 1) / group_size;
   if (ngroups > 60) return fail(STAN_CUDA_ERR_ARG, "launch_glm: grid too large for the ticket block");
-  SC_TRY(workspace_reserve(ws, d->device, size_t(grid + ngroups) * (t.kpad + 4)));
+  SC_TRY(workspace_reserve(ws, d->device, size_t(grid + ngroups) * (t.kpad + 4) + 2));
 
   GlmKernelParams p;
   SC_TRY(fill_kernel_params(d, io, ws, &p));
@@ -289,6 +348,10 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
     case STAN_CUDA_NORMAL_ID:
       return rowio ? launch_warp_inst<STAN_CUDA_NORMAL_ID, true>(p, grid, smem, stream)
                    : launch_warp_inst<STAN_CUDA_NORMAL_ID, false>(p, grid, smem, stream);
+    case STAN_CUDA_NEG_BINOMIAL_2_LOG:
+      SC_TRY(prepare_neg_binomial(d, io, ws, &p, stream));
+      return rowio ? launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, true>(p, grid, smem, stream)
+                   : launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, false>(p, grid, smem, stream);
   }
   return fail(STAN_CUDA_ERR_ARG, "launch_glm: unknown family");
 }

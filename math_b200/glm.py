@@ -4,6 +4,7 @@ Same names, argument order and error behaviour as the reference functions
   bernoulli_logit_glm_lpmf(y, x, alpha, beta)     stan/math/prim/mat/prob/bernoulli_logit_glm_lpmf.hpp:46-49
   poisson_log_glm_lpmf(y, x, alpha, beta)         stan/math/prim/mat/prob/poisson_log_glm_lpmf.hpp:44-49
   normal_id_glm_lpdf(y, x, alpha, beta, sigma)    stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:49-53
+  neg_binomial_2_log_glm_lpmf(y, x, alpha, beta, phi)  stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:60-63
   normal_lpdf(y, mu, sigma)                       stan/math/prim/scal/prob/normal_lpdf.hpp:36-39
 Each returns (lp, grads) where grads holds what reverse mode would leave in the adjoints of the
 var arguments (alpha, beta, sigma, mu; y on request).  Size mismatches raise ValueError
@@ -85,6 +86,18 @@ def glm_flags(family, propto, alpha_var=True, beta_var=True, sigma_var=True, y_v
     """The include_summand<propto, ...> decisions of the three reference bodies, for the given
     constness of the arguments (x is always data on this path)."""
     any_var = alpha_var or beta_var or (family == _abi.NORMAL_ID and (sigma_var or y_var))
+    if family == _abi.NEG_BINOMIAL_2_LOG:      # neg_binomial_2_log_glm_lpmf.hpp:130-153
+        f = (_abi.NEED_DBETA if beta_var else 0) | (_abi.NEED_DALPHA if alpha_var else 0) \
+            | (_abi.NEED_DSIGMA if sigma_var else 0)
+        if not propto:
+            f |= _abi.LP_CONST
+        if not propto or sigma_var:
+            f |= _abi.LP_SCALE
+        if not propto or alpha_var or beta_var or sigma_var:
+            f |= _abi.LP_MAIN
+        if not propto or alpha_var or beta_var:
+            f |= _abi.LP_LINEAR
+        return f
     f = 0
     if beta_var:
         f |= _abi.NEED_DBETA
@@ -141,7 +154,7 @@ def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, ne
     rc = check(lib().stan_cuda_glm_eval(C.byref(a)))
     out = {"rc": rc, "lp": float(lp[0]), "dbeta": dbeta[:k].copy(), "dalpha": dalpha[:alpha.size].copy(),
            "aux": aux, "_keep": (x, y)}
-    if fam == _abi.NORMAL_ID:
+    if fam in _abi.HAS_SCALE:
         out["dsigma"] = dsigma[:sigma.size].copy()
     if dy is not None:
         out["dy"] = dy[:n].copy()
@@ -163,7 +176,7 @@ def _lazy_finite_checks(function, fam, rc, x, y, alpha, beta, sigma):
         raise DomainError("%s: Weight vector is not finite" % function)
     if not np.all(np.isfinite(alpha)):
         raise DomainError("%s: Intercept is not finite" % function)
-    if fam == _abi.NORMAL_ID:
+    if fam in _abi.HAS_SCALE:   # normal_id :150-156; neg_binomial_2_log :120 (whole theta vector checked)
         raise DomainError("%s: Matrix of independent variables is not finite" % function)
     with np.errstate(all="ignore"):
         theta0 = float(np.dot(x[0, :], np.broadcast_to(beta, (x.shape[1],))) + alpha[0])
@@ -182,13 +195,20 @@ def _glm(function, fam, y, x, alpha, beta, sigma, propto, need_dy=False):
     if fam == _abi.NORMAL_ID:
         if not (np.all(np.isfinite(sg)) and np.all(sg > 0)):       # check_positive_finite, :70
             raise DomainError("%s: Scale vector must be positive finite" % function)
+    if fam == _abi.NEG_BINOMIAL_2_LOG:   # eager parameter checks, neg_binomial_2_log_glm_lpmf.hpp:90-92
+        if not np.all(np.isfinite(be)):
+            raise DomainError("%s: Weight vector is not finite" % function)
+        if not np.all(np.isfinite(al)):
+            raise DomainError("%s: Intercept is not finite" % function)
+        if not (np.all(np.isfinite(sg)) and np.all(sg > 0)):
+            raise DomainError("%s: Precision parameter must be positive finite" % function)
     _size_check(function, "Vector of dependent variables", ya, n)
     if be.size != k and not (be.size == 1 and k == 1):
         raise ValueError("%s: Weight vector has dimension = %d, expecting dimension = %d" % (function, be.size, k))
     if sg is not None:
         _size_check(function, "Vector of scale parameters", sg, n)
     _size_check(function, "Vector of intercepts", al, n)
-    if n == 0 or (fam == _abi.NORMAL_ID and sg.size == 0):
+    if n == 0 or (fam in _abi.HAS_SCALE and sg.size == 0):
         return 0.0, {}
     r = glm_eval(fam, ya, xa, al, be, sg, propto=propto, need_dy=need_dy)
     if r["rc"] == _abi.BAD_OUTCOME:
@@ -196,11 +216,15 @@ def _glm(function, fam, y, x, alpha, beta, sigma, propto, need_dy=False):
         # once at cache fill; the host loop runs only here, to word the exception
         if fam == _abi.BERNOULLI_LOGIT:
             raise DomainError("%s: Vector of dependent variables must be in the interval [0, 1]" % function)
+        if fam == _abi.NEG_BINOMIAL_2_LOG:
+            raise DomainError("%s: Failures variables must be >= 0" % function)
         raise DomainError("%s: Vector of dependent variables must be >= 0" % function)
     _lazy_finite_checks(function, fam, r["rc"], xa, ya, al, be, sg)
     grads = {"beta": r["dbeta"], "alpha": r["dalpha"]}
     if fam == _abi.NORMAL_ID:
         grads["sigma"] = r["dsigma"]
+    if fam == _abi.NEG_BINOMIAL_2_LOG:
+        grads["phi"] = r["dsigma"]
     if need_dy:
         grads["y"] = r["dy"]
     return r["lp"], grads
@@ -216,6 +240,11 @@ def poisson_log_glm_lpmf(y, x, alpha, beta, propto=False):
 
 def normal_id_glm_lpdf(y, x, alpha, beta, sigma, propto=False, need_dy=False):
     return _glm("normal_id_glm_lpdf", _abi.NORMAL_ID, y, x, alpha, beta, sigma, propto, need_dy)
+
+
+def neg_binomial_2_log_glm_lpmf(y, x, alpha, beta, phi, propto=False):
+    """stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:60-63; grads: beta, alpha, phi."""
+    return _glm("neg_binomial_2_log_glm_lpmf", _abi.NEG_BINOMIAL_2_LOG, y, x, alpha, beta, phi, propto)
 
 
 def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):

@@ -146,6 +146,72 @@ static int normal_id_glm(const stan_cuda_glm_args* a, double* m) {
   return isfinite(sum_s2) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;              /* :150 */
 }
 
+/* digamma: the reference calls boost::math::digamma (stan/math/prim/scal/fun/digamma.hpp:50-52,
+ * Boost 1.69, absent as a compiled library here but header-only in /root/reference/lib).  Restated
+ * with the textbook algorithm: recurrence psi(x) = psi(x + 1) - 1/x up to x >= 10, then the
+ * asymptotic series ln x - 1/(2x) - sum B_2k / (2k x^2k) (7 terms: error < 1e-17 at x = 10).
+ * Pinned against the compiled reference in tests/test_oracle.py. */
+static double oracle_digamma(double x) {
+  double r = 0.0;
+  while (x < 10.0) {
+    r -= 1.0 / x;
+    x += 1.0;
+  }
+  const double f = 1.0 / (x * x);
+  const double t = f * (-1.0 / 12.0 + f * (1.0 / 120.0 + f * (-1.0 / 252.0 + f * (1.0 / 240.0
+                 + f * (-1.0 / 132.0 + f * (691.0 / 32760.0 + f * (-1.0 / 12.0)))))));
+  return r + log(x) - 0.5 / x + t;
+}
+
+/* stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:108-197; phi arrives in the sigma slot */
+static int neg_binomial_2_log_glm(const stan_cuda_glm_args* a, double* d) {
+  double sum_d = 0.0, lg_y1 = 0.0, scale_term = 0.0, main_term = 0.0, lin_term = 0.0, lg_ypp = 0.0;
+  double dphi_sum = 0.0, witness = 0.0;
+  double* theta = linear_predictor(a);
+  if (!theta) return STAN_CUDA_ERR_ARG;
+  const int phi_vec = a->sigma_len != 1;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const double y = y_at(a, i);
+    const double phi = phi_vec ? a->sigma[i] : a->sigma[0];
+    const double th = theta[i] + (a->alpha_len == 1 ? a->alpha[0] : a->alpha[i]);    /* :118-119 */
+    const double log_phi = log(phi);                                                   /* :121 */
+    const double lse = th > log_phi ? th + log1p(exp(log_phi - th))                    /* :122-125 */
+                                    : log_phi + log1p(exp(th - log_phi));
+    const double ypp = y + phi;                                                        /* :127 */
+    lg_y1 += lgamma(y + 1.0);                                                          /* :131 */
+    if (phi_vec) scale_term += (phi == 0 ? 0.0 : phi * log_phi) - lgamma(phi);         /* :137 */
+    main_term += ypp * lse;                                                            /* :146 */
+    lin_term += y * th;                                                                /* :149 */
+    lg_ypp += lgamma(ypp);                                                             /* :152 */
+    const double te = exp(th);                                                         /* :159 */
+    d[i] = y - te * ypp / (te + phi);                                                  /* :162 */
+    sum_d += d[i];
+    const double dp = -ypp / (te + phi) + log_phi - lse + oracle_digamma(ypp) - oracle_digamma(phi);
+    if (phi_vec) {
+      if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma) a->dsigma[i] = 1.0 + dp;    /* :180-183 */
+    } else {
+      dphi_sum += dp;                                                                  /* :185-190 */
+    }
+    witness += th;
+  }
+  free(theta);
+  if (!phi_vec) {
+    const double phi = a->sigma[0];
+    scale_term = (double)a->n * ((phi == 0 ? 0.0 : phi * log(phi)) - lgamma(phi));     /* :140-142 */
+    if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma) a->dsigma[0] = (double)a->n + dphi_sum; /* :185 */
+  }
+  double logp = 0.0;
+  if (a->flags & STAN_CUDA_LP_CONST) logp -= lg_y1;                                    /* :130-132 */
+  if (a->flags & STAN_CUDA_LP_SCALE) logp += scale_term;                               /* :133-144 */
+  if (a->flags & STAN_CUDA_LP_MAIN) logp -= main_term;                                 /* :145-147 */
+  if (a->flags & STAN_CUDA_LP_LINEAR) logp += lin_term;                                /* :148-150 */
+  if (a->flags & STAN_CUDA_LP_SCALE) logp += lg_ypp;                                   /* :151-153 */
+  if (a->lp) *a->lp = logp;
+  if (a->aux) { a->aux[0] = sum_d; a->aux[1] = witness; a->aux[2] = 0; a->aux[3] = lg_y1; }
+  write_dalpha(a, d, sum_d);
+  return isfinite(witness) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;                       /* :120 check_finite(theta) */
+}
+
 int oracle_glm_eval(const stan_cuda_glm_args* a) {
   if (!a || a->n < 0 || a->k < 0) return STAN_CUDA_ERR_ARG;
   if (a->alpha_len != 1 && a->alpha_len != a->n) return STAN_CUDA_ERR_ARG;
@@ -158,6 +224,10 @@ int oracle_glm_eval(const stan_cuda_glm_args* a) {
     case STAN_CUDA_NORMAL_ID:
       if (a->sigma_len != 1 && a->sigma_len != a->n) { free(d); return STAN_CUDA_ERR_ARG; }
       rc = normal_id_glm(a, d);
+      break;
+    case STAN_CUDA_NEG_BINOMIAL_2_LOG:
+      if (a->sigma_len != 1 && a->sigma_len != a->n) { free(d); return STAN_CUDA_ERR_ARG; }
+      rc = neg_binomial_2_log_glm(a, d);
       break;
     default: free(d); return STAN_CUDA_ERR_ARG;
   }

@@ -124,7 +124,7 @@ def glm_args(fam, x, y, alpha, beta, sigma, flags, need_dy=False):
 def _finish_glm(rc, out, fam, n, k, alpha, sigma):
     res = {"rc": rc, "lp": float(out["lp"][0]), "dbeta": out["dbeta"][:k].copy(),
            "dalpha": out["dalpha"][:alpha.size].copy(), "aux": out["aux"].copy()}
-    if fam == _abi.NORMAL_ID and sigma is not None:
+    if fam in _abi.HAS_SCALE and sigma is not None:
         res["dsigma"] = out["dsigma"][:sigma.size].copy()
     if out["dy"] is not None:
         res["dy"] = out["dy"][:n].copy()
@@ -137,6 +137,10 @@ def flags_for(fam, propto=False, need_dy=False):
     and (include_summand<propto, double>) the main term, poisson_log_glm_lpmf.hpp:102-112;
     normal_id<propto=true> drops N*NEG_LOG_SQRT_TWO_PI, normal_id_glm_lpdf.hpp:160-172."""
     f = _abi.NEED_DBETA | _abi.NEED_DALPHA | _abi.NEED_DSIGMA | (_abi.NEED_DY if need_dy else 0)
+    if fam == _abi.NEG_BINOMIAL_2_LOG:
+        # with every parameter a var only the lgamma(y + 1) term depends on propto
+        # (neg_binomial_2_log_glm_lpmf.hpp:130-153)
+        return f | _abi.LP_SCALE | _abi.LP_MAIN | _abi.LP_LINEAR | (0 if propto else _abi.LP_CONST)
     if not propto:
         return f | _abi.LP_ALL
     if fam == _abi.BERNOULLI_LOGIT:
@@ -180,7 +184,7 @@ def ref_glm(family, x, y, alpha, beta, sigma=None, propto=False, need_dy=False):
         raise RefError(rc, err.value.decode())
     res = {"rc": 0, "lp": float(lp[0]), "dbeta": dbeta[:k].copy(), "dalpha": dalpha[:alpha.size].copy(),
            "seconds": float(secs[0])}
-    if fam == _abi.NORMAL_ID:
+    if fam in _abi.HAS_SCALE:
         res["dsigma"] = dsigma[:sg.size].copy()
     if need_dy:
         res["dy"] = dy[:n].copy()

@@ -14,6 +14,7 @@
 //   poisson_log_glm_lpmf      stan/math/prim/mat/prob/poisson_log_glm_lpmf.hpp:44-131
 //   normal_id_glm_lpdf        stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:49-174
 //   normal_lpdf               stan/math/prim/scal/prob/normal_lpdf.hpp:36-112
+//   neg_binomial_2_log_glm_lpmf stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:60-197
 //   map_rect                  stan/math/prim/mat/functor/map_rect.hpp:120-177
 #include <stan/math.hpp>
 
@@ -30,7 +31,7 @@ typedef Eigen::Matrix<var, Eigen::Dynamic, 1> vector_v;
 typedef Eigen::Matrix<double, Eigen::Dynamic, 1> vector_d;
 typedef Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic> matrix_d;
 
-enum { FAM_BERNOULLI_LOGIT = 0, FAM_POISSON_LOG = 1, FAM_NORMAL_ID = 2 };
+enum { FAM_BERNOULLI_LOGIT = 0, FAM_POISSON_LOG = 1, FAM_NORMAL_ID = 2, FAM_NEG_BINOMIAL_2_LOG = 3 };
 
 void set_err(char* err, int errlen, const char* what) {
   if (err && errlen > 0) {
@@ -80,6 +81,8 @@ var call_family(int family, const T_y& y, const std::vector<int>& yi,
       return stan::math::bernoulli_logit_glm_lpmf<propto>(yi, x, alpha, beta);
     case FAM_POISSON_LOG:
       return stan::math::poisson_log_glm_lpmf<propto>(yi, x, alpha, beta);
+    case FAM_NEG_BINOMIAL_2_LOG:  // the precision phi travels in the sigma slot
+      return stan::math::neg_binomial_2_log_glm_lpmf<propto>(yi, x, alpha, beta, sigma);
     default:
       return stan::math::normal_id_glm_lpdf<propto>(y, x, alpha, beta, sigma);
   }
@@ -115,11 +118,12 @@ int stanref_glm(int family, int propto, long n, long k, const double* x,
         }
         vector_v beta_v = make_vars(beta, k);
         vector_v alpha_vec = make_vars(alpha, alpha_len);
-        vector_v sigma_vec = make_vars(sigma, family == FAM_NORMAL_ID ? sigma_len : 0);
+        const bool has_scale = family == FAM_NORMAL_ID || family == FAM_NEG_BINOMIAL_2_LOG;
+        vector_v sigma_vec = make_vars(sigma, has_scale ? sigma_len : 0);
         vector_v y_v = make_vars(yd.data(), y_is_var ? n : 0);
         auto t0 = std::chrono::steady_clock::now();
         var res;
-        const bool av = alpha_len != 1, sv = (family == FAM_NORMAL_ID && sigma_len != 1);
+        const bool av = alpha_len != 1, sv = (has_scale && sigma_len != 1);
         var a0 = alpha_len >= 1 ? alpha_vec[0] : var(0.0);
         var s0 = sigma_vec.size() >= 1 ? sigma_vec[0] : var(1.0);
 #define STANREF_CALL(P, YARG)                                                        \
@@ -141,7 +145,7 @@ int stanref_glm(int family, int propto, long n, long k, const double* x,
         if (dalpha) {
           if (av) read_adj(alpha_vec, dalpha); else dalpha[0] = a0.adj();
         }
-        if (dsigma && family == FAM_NORMAL_ID) {
+        if (dsigma && has_scale) {
           if (sv) read_adj(sigma_vec, dsigma); else dsigma[0] = s0.adj();
         }
         if (dy && y_is_var) read_adj(y_v, dy);

@@ -127,6 +127,15 @@ TEST_P(CudaGlm, bernoulli_poisson_normal_match_reference_body) {
   STAN_CUDA_PARITY("normal_id propto", normal_id_glm_lpdf<true>(p.y_norm, p.x, alpha, beta, sigma),
                    normal_id_glm_lpdf_reference_cpu<true>(p.y_norm, p.x, alpha, beta, sigma), adj(beta),
                    VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, sigma.adj()));
+  var phi = 2.5;
+  std::vector<int> y_nb = p.y_pois;
+  for (size_t i = 0; i < y_nb.size(); ++i) y_nb[i] = (y_nb[i] * 7 + static_cast<int>(i % 5)) % 200;
+  STAN_CUDA_PARITY("neg_binomial_2_log", neg_binomial_2_log_glm_lpmf(y_nb, p.x, alpha, beta, phi),
+                   neg_binomial_2_log_glm_lpmf_reference_cpu(y_nb, p.x, alpha, beta, phi), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, phi.adj()));
+  STAN_CUDA_PARITY("neg_binomial_2_log propto", neg_binomial_2_log_glm_lpmf<true>(y_nb, p.x, alpha, beta, phi),
+                   neg_binomial_2_log_glm_lpmf_reference_cpu<true>(y_nb, p.x, alpha, beta, phi), adj(beta),
+                   VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, phi.adj()));
   // all-double call returns a double through the same device path
   EXPECT_NEAR(poisson_log_glm_lpmf(p.y_pois, p.x, p.alpha, p.beta),
               poisson_log_glm_lpmf_reference_cpu(p.y_pois, p.x, p.alpha, p.beta),
@@ -150,6 +159,10 @@ TEST(CudaGlmVariants, vector_alpha_vector_sigma_var_y) {
   STAN_CUDA_PARITY("normal all vectors + var y", normal_id_glm_lpdf(y_v, p.x, alpha_v, beta, sigma_v),
                    normal_id_glm_lpdf_reference_cpu(y_v, p.x, alpha_v, beta, sigma_v), adj(beta), adj(alpha_v),
                    adj(sigma_v), adj(y_v));
+  vector_v phi_v = to_v(p.sigma_vec);
+  STAN_CUDA_PARITY("neg_binomial_2_log vector alpha and phi", neg_binomial_2_log_glm_lpmf(p.y_pois, p.x, alpha_v, beta, phi_v),
+                   neg_binomial_2_log_glm_lpmf_reference_cpu(p.y_pois, p.x, alpha_v, beta, phi_v), adj(beta),
+                   adj(alpha_v), adj(phi_v));
   // std::vector<var> and row-vector operands
   std::vector<var> beta_std(p.beta.data(), p.beta.data() + p.beta.size());
   Matrix<var, 1, Dynamic> beta_row = beta.transpose();
@@ -218,12 +231,19 @@ TEST(CudaGlmErrors, same_exceptions_as_the_reference) {
   EXPECT_THROW(poisson_log_glm_lpmf(y, x, alpha, beta_inf), std::domain_error);
   EXPECT_THROW(poisson_log_glm_lpmf(y, x, NAN, beta), std::domain_error);
   EXPECT_THROW(normal_id_glm_lpdf(yn, x, alpha, beta, 0.0), std::domain_error);
+  using stan::math::neg_binomial_2_log_glm_lpmf;
+  EXPECT_THROW(neg_binomial_2_log_glm_lpmf(y_size, x, alpha, beta, 2.0), std::invalid_argument);
+  EXPECT_THROW(neg_binomial_2_log_glm_lpmf(y_neg, x, alpha, beta, 2.0), std::domain_error);
+  EXPECT_THROW(neg_binomial_2_log_glm_lpmf(y, x, alpha, beta_inf, 2.0), std::domain_error);
+  EXPECT_THROW(neg_binomial_2_log_glm_lpmf(y, x, alpha, beta, 0.0), std::domain_error);
+  EXPECT_THROW(neg_binomial_2_log_glm_lpmf(y, x, NAN, beta, 2.0), std::domain_error);
   EXPECT_THROW(normal_id_glm_lpdf(yn, x, alpha, beta, INFINITY), std::domain_error);
   MatrixXd x_bad = x;
   x_bad(0, 1) = NAN;
   EXPECT_THROW(bernoulli_logit_glm_lpmf(y, x_bad, alpha, beta), std::domain_error);
   EXPECT_THROW(poisson_log_glm_lpmf(y, x_bad, alpha, beta), std::domain_error);
   EXPECT_THROW(normal_id_glm_lpdf(yn, x_bad, alpha, beta, 1.0), std::domain_error);
+  EXPECT_THROW(neg_binomial_2_log_glm_lpmf(y, x_bad, alpha, beta, 1.0), std::domain_error);
   // messages agree with the reference body on the lazy path
   std::string m_gpu, m_cpu;
   try {

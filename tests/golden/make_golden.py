@@ -111,6 +111,30 @@ add_normal("vec_mu_propto", yv, 0.1 * rng.standard_normal(1000), [1.3], propto=T
 add_normal("vec_all_dy", yv, 0.1 * rng.standard_normal(1000), 0.5 + rng.random(1000), need_dy=True)
 add_normal("scalar_mu", yv, [0.25], [0.8])
 
+# neg_binomial_2_log_glm (added after everything above so the earlier draws are unchanged):
+# the fixed fixture of test/unit/math/rev/mat/prob/neg_binomial_2_log_glm_lpmf_test.cpp:13-30
+# (x = [-12 46; -42 24; 25 27], beta = (0.3, 2), alpha = 0.3, phi = 2, y = {1, 0, 1}) scaled like
+# the poisson fixture, large counts (% 200 in the reference's random test), vector alpha / phi
+rng2 = np.random.default_rng(20191105)
+for propto in (False, True):
+    s = "_propto" if propto else ""
+    add_glm("nb_fixture" + s, "neg_binomial_2_log", X * 0.01, [1, 0, 1], ALPHA, BETA, [2.0], propto=propto)
+    add_glm("nb_fixture2" + s, "neg_binomial_2_log", X * 0.01, [14, 2, 5], ALPHA, BETA, [2.0], propto=propto)
+for n, k, tag in ((153, 71, "nbbig"), (600, 128, "nbwide"), (1000, 1, "nbk1")):
+    x = rng2.standard_normal((n, k))
+    bt = rng2.standard_normal(k) * (0.6 / np.sqrt(k))
+    beta = bt + rng2.standard_normal(k) * 0.05
+    eta = 0.2 + x @ bt
+    yc = rng2.negative_binomial(3.0, 3.0 / (3.0 + np.exp(eta)))
+    add_glm("nb_" + tag, "neg_binomial_2_log", x, yc, 0.3, beta, [2.5], xkey=tag)
+    if tag == "nbbig":
+        av = 0.3 + 0.1 * rng2.standard_normal(n)
+        pv = 0.5 + 4 * rng2.random(n)
+        add_glm("nb_big_valpha", "neg_binomial_2_log", x, yc, av, beta, [0.7], xkey=tag)
+        add_glm("nb_big_vphi", "neg_binomial_2_log", x, yc, 0.3, beta, pv, xkey=tag)
+        add_glm("nb_big_valpha_vphi_propto", "neg_binomial_2_log", x, yc, av, beta, pv, propto=True, xkey=tag)
+        add_glm("nb_big_counts", "neg_binomial_2_log", x, rng2.integers(0, 200, n), 0.3, beta, [1.5], xkey=tag)
+
 out["glm_cases"] = np.array(names)
 out["normal_cases"] = np.array(nl)
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "glm_golden.npz")

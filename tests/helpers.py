@@ -27,9 +27,9 @@ def glm_case(golden, name):
     fam = int(golden[p + "family"])
     c = {"family": fam, "propto": bool(golden[p + "propto"]), "need_dy": bool(golden[p + "need_dy"]),
          "x": golden["x/" + str(golden[p + "xkey"])], "y": golden[p + "y"], "alpha": golden[p + "alpha"],
-         "beta": golden[p + "beta"], "sigma": golden[p + "sigma"] if fam == _abi.NORMAL_ID else None,
+         "beta": golden[p + "beta"], "sigma": golden[p + "sigma"] if fam in _abi.HAS_SCALE else None,
          "lp": float(golden[p + "lp"]), "dbeta": golden[p + "dbeta"], "dalpha": golden[p + "dalpha"]}
-    if fam == _abi.NORMAL_ID:
+    if fam in _abi.HAS_SCALE:
         c["dsigma"] = golden[p + "dsigma"]
     if c["need_dy"]:
         c["dy"] = golden[p + "dy"]
@@ -70,8 +70,10 @@ def synth_glm(family, n, k, seed, dtype_y=None):
         y = (rng.random(n) < 1.0 / (1.0 + np.exp(-eta))).astype(np.int32)
     elif fam == _abi.POISSON_LOG:
         y = rng.poisson(np.exp(eta)).astype(np.int32)
+    elif fam == _abi.NEG_BINOMIAL_2_LOG:
+        y = rng.negative_binomial(3.0, 3.0 / (3.0 + np.exp(eta))).astype(np.int32)
     else:
         y = eta + 0.7 * rng.standard_normal(n)
     beta = beta_true + 0.02 * rng.standard_normal(k)
     return {"family": fam, "x": x, "y": y, "alpha": np.array([0.3]), "beta": beta,
-            "sigma": np.array([1.0]) if fam == _abi.NORMAL_ID else None}
+            "sigma": np.array([1.0]) if fam == _abi.NORMAL_ID else (np.array([2.5]) if fam == _abi.NEG_BINOMIAL_2_LOG else None)}

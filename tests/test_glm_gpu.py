@@ -64,7 +64,7 @@ SHAPES = [(1, 1), (5, 2), (33, 7), (1000, 16), (4097, 33), (100000, 32), (30011,
           (777, 100)]
 
 
-@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id"])
+@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id", "neg_binomial_2_log"])
 @pytest.mark.parametrize("n,k", SHAPES)
 def test_against_oracle(glm, L, family, n, k):
     s = synth_glm(family, n, k, seed=7 * n + k)
@@ -75,13 +75,13 @@ def test_against_oracle(glm, L, family, n, k):
         check_glm_result(got, ref, "%s %dx%d propto=%s" % (family, n, k, propto))
 
 
-@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id"])
+@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id", "neg_binomial_2_log"])
 def test_vector_alpha_sigma_and_dy(glm, L, family):
     n, k = 5003, 40
     s = synth_glm(family, n, k, seed=99)
     rng = np.random.default_rng(3)
     alpha = 0.3 + 0.1 * rng.standard_normal(n)
-    sigma = 0.5 + rng.random(n) if family == "normal_id" else None
+    sigma = 0.5 + rng.random(n) if family in ("normal_id", "neg_binomial_2_log") else None
     need_dy = family == "normal_id"
     ref = L.oracle_glm(family, s["x"], s["y"], alpha, s["beta"], sigma, need_dy=need_dy)
     got = glm.glm_eval(family, s["y"], s["x"], alpha, s["beta"], sigma, need_dy=need_dy)
@@ -138,6 +138,39 @@ def test_error_contract_lazy_checks(glm):
     xi[2, 0] = np.nan
     lp, _ = glm.bernoulli_logit_glm_lpmf([1, 0, 1], xi, 0.3, [0.1, 0.2])
     assert np.isnan(lp)
+
+
+def test_neg_binomial_2_log_histogram_and_per_row_paths_agree(glm, L):
+    """Scalar phi uses the histogram of y built at fill (sum lgamma / digamma over distinct counts);
+    a constant vector phi forces the per-row special functions.  Same numbers, and the wrapper's
+    error contract (neg_binomial_2_log_glm_lpmf.hpp:88-92,120)."""
+    s = synth_glm("neg_binomial_2_log", 20011, 24, seed=31)
+    ref = L.oracle_glm("neg_binomial_2_log", s["x"], s["y"], s["alpha"], s["beta"], [1.7])
+    a = glm.glm_eval("neg_binomial_2_log", s["y"], s["x"], s["alpha"], s["beta"], [1.7])
+    b = glm.glm_eval("neg_binomial_2_log", s["y"], s["x"], s["alpha"], s["beta"], np.full(20011, 1.7))
+    check_glm_result(a, ref, "nb scalar phi")
+    assert_close(b["lp"], ref["lp"], "nb vector phi lp")
+    assert_close(b["dbeta"], ref["dbeta"], "nb vector phi dbeta")
+    assert_close(np.sum(b["dsigma"]), ref["dsigma"][0], "nb sum of per-row dphi", 1e-9)
+    lp, g = glm.neg_binomial_2_log_glm_lpmf(s["y"], s["x"], 0.3, s["beta"], 1.7)
+    assert_close(lp, ref["lp"], "nb wrapper lp")
+    assert_close(g["phi"], ref["dsigma"], "nb wrapper dphi")
+    lp_p, _ = glm.neg_binomial_2_log_glm_lpmf(s["y"], s["x"], 0.3, s["beta"], 1.7, propto=True)
+    ref_p = L.oracle_glm("neg_binomial_2_log", s["x"], s["y"], s["alpha"], s["beta"], [1.7], propto=True)
+    assert_close(lp_p, ref_p["lp"], "nb propto lp")
+    with pytest.raises(glm.DomainError, match="Precision"):
+        glm.neg_binomial_2_log_glm_lpmf(s["y"], s["x"], 0.3, s["beta"], 0.0)
+    with pytest.raises(glm.DomainError, match="Weight"):
+        glm.neg_binomial_2_log_glm_lpmf(s["y"], s["x"], 0.3, s["beta"] * np.inf, 1.0)
+    ybad = s["y"].copy()
+    ybad[5] = -1
+    with pytest.raises(glm.DomainError, match="Failures"):
+        glm.neg_binomial_2_log_glm_lpmf(ybad, s["x"], 0.3, s["beta"], 1.0)
+    xbad = s["x"].copy()
+    xbad[100, 3] = np.inf
+    with pytest.raises(glm.DomainError, match="independent"):
+        glm.neg_binomial_2_log_glm_lpmf(s["y"], xbad, 0.3, s["beta"], 1.0)
+    glm.cache_clear()
 
 
 def test_outcome_domain_is_checked_on_the_device_at_fill(glm):
