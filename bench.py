@@ -353,7 +353,7 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": desc, "family": family, "n": n, "k": k, "rows_per_gpu": rows,
-                       "parallelism": ("rows/%d + %s(%d f64)" % (world, "all-reduce fused into glm_fused_kernel over NVLink peer memory"
+                       "parallelism": ("rows/%d + %s(%d f64)" % (world, "all-reduce fused into the GLM kernel over NVLink peer memory"
                                                                  if fused else "ncclAllReduce", data.result_len)) if world > 1 else "1 GPU",
                        "l2": "no flush: per-GPU input %.2f GB is larger than the 126 MB L2" % (alg_bytes / 1e9)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
