@@ -16,6 +16,7 @@
  *                                  stan/math/opencl/kernels/{bernoulli_logit,poisson_log,normal_id}_glm_*.hpp
  *                                  stan/math/opencl/kernels/matrix_multiply.hpp:354-386 (row_vector_matrix_multiply)
  *                                  neg_binomial_2_log_glm_lpmf stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:108-197
+ *                                  ordered_logistic_glm_lpmf   stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:93-199
  *   stan_cuda_normal_lpdf_eval   the loop of normal_lpdf      stan/math/prim/scal/prob/normal_lpdf.hpp:67-110
  *   stan_cuda_data_* / cache_*   matrix_cl + to_matrix_cl      stan/math/opencl/matrix_cl.hpp:32-454, stan/math/opencl/copy.hpp:37-93
  *                                and the cache-by-call_id of the MPI backend
@@ -33,7 +34,8 @@
  *                             the same std::domain_error is thrown (bernoulli_logit_glm_lpmf.hpp:106-110)
  *    2  STAN_CUDA_BAD_OUTCOME the device-resident outcome vector violates the family's domain (bernoulli:
  *                             outside [0, 1], bernoulli_logit_glm_lpmf.hpp:70; poisson: negative,
- *                             poisson_log_glm_lpmf.hpp:70).  The range of y is computed ONCE, on the device,
+ *                             poisson_log_glm_lpmf.hpp:70; ordered_logistic: outside [1, cuts_len + 1],
+ *                             ordered_logistic_glm_lpmf.hpp:78).  The range of y is computed ONCE, on the device,
  *                             when y is cached (the data is immutable), so the per-call O(N) host loop of
  *                             check_bounded / check_nonnegative disappears; nothing was evaluated; the C++
  *                             wrapper runs the reference's own check to throw the same std::domain_error
@@ -78,6 +80,7 @@ extern "C" {
 #define STAN_CUDA_POISSON_LOG 1
 #define STAN_CUDA_NORMAL_ID 2
 #define STAN_CUDA_NEG_BINOMIAL_2_LOG 3 /* precision phi travels in the sigma slot, d/dphi in dsigma */
+#define STAN_CUDA_ORDERED_LOGISTIC 4   /* no intercept; cut-points in cuts[cuts_len], d/dcuts in dcuts; y in 1..cuts_len+1 */
 
 /* flags: which summands of the log-density to include (the reference decides this at compile
  * time with include_summand<propto, ...>, stan/math/prim/scal/meta/include_summand.hpp) and
@@ -93,6 +96,7 @@ extern "C" {
 #define STAN_CUDA_NEED_DBETA 0x08u
 #define STAN_CUDA_NEED_DALPHA 0x10u /* GLM: d/dalpha ; normal_lpdf: d/dmu                          */
 #define STAN_CUDA_NEED_DSIGMA 0x20u
+#define STAN_CUDA_NEED_DCUTS 0x20u  /* ordered_logistic: d/dcuts (shares the bit of NEED_DSIGMA)  */
 #define STAN_CUDA_NEED_DY 0x40u
 #define STAN_CUDA_NEED_ALL 0x78u
 /* stan_cuda_glm_launch only: sum the result block over the ranks of the communicator INSIDE the
@@ -101,7 +105,7 @@ extern "C" {
 #define STAN_CUDA_FUSED_ALLREDUCE 0x100u
 
 typedef struct stan_cuda_glm_args {
-  int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID | NEG_BINOMIAL_2_LOG */
+  int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID | NEG_BINOMIAL_2_LOG | ORDERED_LOGISTIC */
   uint32_t flags;      /* STAN_CUDA_LP_* | STAN_CUDA_NEED_* */
   int64_t n;           /* rows of x (instances) */
   int64_t k;           /* columns of x (attributes) */
@@ -110,7 +114,7 @@ typedef struct stan_cuda_glm_args {
   int32_t x_row_major; /* 0 = column-major (Eigen::MatrixXd), 1 = row-major */
   int32_t y_is_double; /* 0: y is int32[n] (bernoulli, poisson); 1: y is double[n] */
   const void* y;       /* host, borrowed; cached with x */
-  const double* alpha; /* host; alpha_len doubles */
+  const double* alpha; /* host; alpha_len doubles (ordered_logistic: ignored, may be NULL) */
   int64_t alpha_len;   /* 1 (scalar intercept) or n */
   const double* beta;  /* host; k doubles */
   const double* sigma; /* host; normal_id: scale sigma; neg_binomial_2_log: precision phi */
@@ -122,6 +126,10 @@ typedef struct stan_cuda_glm_args {
   double* dsigma;      /* [sigma_len] */
   double* dy;          /* [n], normal_id only */
   double* aux;         /* optional [4]: sum d, sum s^2, sum log sigma, sum lgamma(y+1) */
+  /* ordered_logistic only (stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:46-52) */
+  const double* cuts;  /* host; cuts_len ascending cut-points (number of classes - 1) */
+  int64_t cuts_len;
+  double* dcuts;       /* [cuts_len] */
 } stan_cuda_glm_args;
 
 typedef struct stan_cuda_normal_args {
@@ -233,6 +241,10 @@ STAN_CUDA_API int stan_cuda_data_y_range(stan_cuda_data_t d, int64_t* y_min, int
 STAN_CUDA_API int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params,
                          const double* d_alpha_vec, const double* d_sigma_vec, double* d_result,
                          double* d_row_dalpha, double* d_row_dsigma, void* stream);
+/* ordered_logistic: d_params = [beta(k_pad), 0, 0, cuts(ncuts)], d_result = [lp, sum_d, 0, status,
+ * dbeta(k_pad), dcuts(ncuts)]; the caller has checked 1 <= y <= ncuts + 1 (stan_cuda_data_y_range). */
+STAN_CUDA_API int stan_cuda_glm_launch_ordered(stan_cuda_data_t d, uint32_t flags, const double* d_params, int ncuts,
+                                 double* d_result, void* stream);
 /* All-reduce (sum) `count` doubles in place across the ranks of the communicator, on `stream`. */
 STAN_CUDA_API int stan_cuda_allreduce(double* d_buf, int64_t count, void* stream);
 /* Number of this library's kernels launched per stan_cuda_glm_launch call for this data. */

@@ -9,14 +9,15 @@ import ctypes as C
 OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND = 0, 1, 2, 3
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
 
-BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID, NEG_BINOMIAL_2_LOG = 0, 1, 2, 3
+BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID, NEG_BINOMIAL_2_LOG, ORDERED_LOGISTIC = 0, 1, 2, 3, 4
 FAMILIES = {"bernoulli_logit": BERNOULLI_LOGIT, "poisson_log": POISSON_LOG, "normal_id": NORMAL_ID,
-            "neg_binomial_2_log": NEG_BINOMIAL_2_LOG}
+            "neg_binomial_2_log": NEG_BINOMIAL_2_LOG, "ordered_logistic": ORDERED_LOGISTIC}
 HAS_SCALE = (NORMAL_ID, NEG_BINOMIAL_2_LOG)   # families with a fifth operand (sigma | phi)
 
 LP_CONST, LP_SCALE, LP_MAIN, LP_ALL = 0x01, 0x02, 0x04, 0x07
 LP_LINEAR = 0x200
 NEED_DBETA, NEED_DALPHA, NEED_DSIGMA, NEED_DY, NEED_ALL = 0x08, 0x10, 0x20, 0x40, 0x78
+NEED_DCUTS = 0x20
 FUSED_ALLREDUCE = 0x100
 
 c_double_p = C.POINTER(C.c_double)
@@ -44,6 +45,9 @@ class GlmArgs(C.Structure):
         ("dsigma", C.c_void_p),
         ("dy", C.c_void_p),
         ("aux", C.c_void_p),
+        ("cuts", C.c_void_p),
+        ("cuts_len", C.c_int64),
+        ("dcuts", C.c_void_p),
     ]
 
 
@@ -113,6 +117,7 @@ PROTOTYPES = {
     "stan_cuda_data_algorithmic_bytes": (C.c_int64, [C.c_void_p]),
     "stan_cuda_glm_launch": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "stan_cuda_glm_launch_ordered": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "stan_cuda_allreduce": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p]),
     "stan_cuda_data_launches_per_eval": (C.c_int, [C.c_void_p]),
     "stan_cuda_data_y_range": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

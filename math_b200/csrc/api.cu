@@ -162,12 +162,17 @@ static inline bool has_scale(int family) {
 
 static int check_glm_args(const stan_cuda_glm_args* a) {
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null args");
-  if (a->family < 0 || a->family > 3) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: unknown family");
+  if (a->family < 0 || a->family > STAN_CUDA_ORDERED_LOGISTIC) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: unknown family");
   if (a->n < 0 || a->k < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: negative size");
   if (a->n > 0 && (!a->y || (!a->x && a->k > 0))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null x or y");
   if (a->k > 0 && !a->beta) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null beta");
-  if (!a->alpha || (a->alpha_len != 1 && a->alpha_len != a->n))
+  if (a->family == STAN_CUDA_ORDERED_LOGISTIC) {
+    if (a->cuts_len < 0 || (a->cuts_len > 0 && !a->cuts)) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null cuts");
+    if (a->cuts_len > kMaxCuts)
+      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: ordered_logistic supports at most 256 cut-points on the device");
+  } else if (!a->alpha || (a->alpha_len != 1 && a->alpha_len != a->n)) {
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: alpha_len must be 1 or n");
+  }
   if (has_scale(a->family)) {
     if (!a->sigma || (a->sigma_len != 1 && a->sigma_len != a->n))
       return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: sigma_len must be 1 or n");
@@ -201,8 +206,11 @@ int glm_eval(const stan_cuda_glm_args* a) {
   if (a->n == 0) {  // size_zero(y): the reference returns 0 before touching anything (:72-74)
     if (a->lp) *a->lp = 0.0;
     if (a->dbeta) for (int64_t j = 0; j < a->k; ++j) a->dbeta[j] = 0.0;
+    if (a->family == STAN_CUDA_ORDERED_LOGISTIC && a->dcuts) for (int64_t j = 0; j < a->cuts_len; ++j) a->dcuts[j] = 0.0;
     return STAN_CUDA_OK;
   }
+  const bool ordered = a->family == STAN_CUDA_ORDERED_LOGISTIC;
+  const size_t ncuts = ordered ? size_t(a->cuts_len) : 0;
   SC_TRY(ensure_init());
   std::shared_ptr<Entry> e;
   SC_TRY(get_glm_entry(a, &e));
@@ -215,9 +223,13 @@ int glm_eval(const stan_cuda_glm_args* a) {
       lo = std::min(lo, e->shards[s].d->y_min);
       hi = std::max(hi, e->shards[s].d->y_max);
     }
-    if (lo < 0 || (a->family == STAN_CUDA_BERNOULLI_LOGIT && hi > 1)) return STAN_CUDA_BAD_OUTCOME;
+    if (ordered) {  // ordered_logistic_glm_lpmf.hpp:78 check_bounded(y, 1, N_classes)
+      if (lo < 1 || hi > int64_t(ncuts) + 1) return STAN_CUDA_BAD_OUTCOME;
+    } else if (lo < 0 || (a->family == STAN_CUDA_BERNOULLI_LOGIT && hi > 1)) {
+      return STAN_CUDA_BAD_OUTCOME;
+    }
   }
-  const bool alpha_vec = a->alpha_len != 1;
+  const bool alpha_vec = !ordered && a->alpha_len != 1;
   const bool sigma_vec = has_scale(a->family) && a->sigma_len != 1;
   const bool want_rowa = ((a->flags & STAN_CUDA_NEED_DALPHA) && alpha_vec && a->dalpha) ||
                          ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID);
@@ -244,7 +256,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
 
   std::vector<ShardRun> runs(S);
   const int kpad = e->shards[0].d->t.kpad;
-  const size_t np = size_t(kpad) + 2, nr = size_t(kpad) + 4;
+  const size_t np = size_t(kpad) + 2 + ncuts, nr = size_t(kpad) + 4 + ncuts;
   // Low-latency path (no per-row vectors in or out, and no separate collective behind the kernel):
   // the parameter block travels in the kernel arguments, the kernel writes the result block and a
   // completion flag straight into mapped pinned host memory, the host spins on the flag.  Saves the
@@ -276,7 +288,8 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (want_rows) { run.d_rows = p; p += rows_al; }
     double* hp = td->h_pinned;
     for (int j = 0; j < kpad; ++j) hp[j] = j < a->k ? a->beta[j] : 0.0;
-    hp[kpad] = alpha_vec ? 0.0 : a->alpha[0];
+    hp[kpad] = (alpha_vec || ordered) ? 0.0 : a->alpha[0];
+    for (size_t j = 0; j < ncuts; ++j) hp[kpad + 2 + j] = a->cuts[j];
     hp[kpad + 1] = (has_scale(a->family) && !sigma_vec) ? a->sigma[0] : 1.0;
     if (!low_latency)
       SC_CUDA(cudaMemcpyAsync(run.d_params, hp, np * sizeof(double), cudaMemcpyHostToDevice, td->stream));
@@ -285,6 +298,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (sigma_vec)
       SC_CUDA(cudaMemcpyAsync(run.d_sigma, a->sigma + r0, size_t(rows) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     LaunchIO io{a->flags, run.d_params, run.d_alpha, run.d_sigma, run.d_result, run.d_rowa, run.d_rows};
+    io.ncuts = int(ncuts);
     if (xchg) {
       io.xchg = S > 1 ? &xchg[s] : xchg;
       io.xchg_seq = xchg_seq;
@@ -357,7 +371,8 @@ int glm_eval(const stan_cuda_glm_args* a) {
   const double* res = runs[0].td->h_pinned + np;
   if (a->lp) *a->lp = res[0];
   if ((a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) memcpy(a->dbeta, res + 4, size_t(a->k) * sizeof(double));
-  if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha && !alpha_vec) a->dalpha[0] = res[1];
+  if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha && !alpha_vec && !ordered) a->dalpha[0] = res[1];
+  if (ordered && (a->flags & STAN_CUDA_NEED_DCUTS) && a->dcuts) memcpy(a->dcuts, res + 4 + kpad, ncuts * sizeof(double));
   if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma && has_scale(a->family) && !sigma_vec)
     a->dsigma[0] = res[2];
   if ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID) {

@@ -108,7 +108,11 @@ struct LaunchIO {
   const double* h_params_inline = nullptr;   // host pointer, params_len doubles, <= kInlineParams
   unsigned long long* host_flag = nullptr;   // device-visible address of the flag
   unsigned long long host_seq = 0;           // value to store
+  // ordered_logistic: cut-points follow the parameter block (d_params[kpad + 2 + j]), d/dcuts follow
+  // the result block (d_result[kpad + 4 + j])
+  int ncuts = 0;
 };
+constexpr int kMaxCuts = 256;                // ordered_logistic: per-warp bins live in shared memory
 constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sigma)
 
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.

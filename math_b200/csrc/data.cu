@@ -247,7 +247,7 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
                     int x_row_major, const void* y, int y_is_double, int64_t row0, cudaStream_t stream,
                     stan_cuda_data** out) {
   if (n_rows <= 0 || k < 0 || (!x && k > 0) || !y) return fail(STAN_CUDA_ERR_ARG, "data block: bad shape or null pointer");
-  if (family < 0 || family > 3) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
+  if (family < 0 || family > STAN_CUDA_ORDERED_LOGISTIC) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
   stan_cuda_data* d = new stan_cuda_data();
   d->device = device;
   d->family = family;
@@ -255,7 +255,7 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
   d->k = k;
   d->y_is_double = y_is_double;
   // neg_binomial_2_log exists on the warp kernel only
-  if (!choose_tiling(n_rows, k, 0, &d->t, family == STAN_CUDA_NEG_BINOMIAL_2_LOG ? kLayoutWarp : -1)) {
+  if (!choose_tiling(n_rows, k, 0, &d->t, family >= STAN_CUDA_NEG_BINOMIAL_2_LOG ? kLayoutWarp : -1)) {
     delete d;
     return fail(STAN_CUDA_ERR_ARG, "data block: k > 512 is outside the fused kernel's range");
   }
@@ -324,12 +324,8 @@ int stan_cuda_data_y_range(stan_cuda_data_t d, int64_t* y_min, int64_t* y_max) {
   return STAN_CUDA_OK;
 }
 
-int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params, const double* d_alpha_vec,
-                         const double* d_sigma_vec, double* d_result, double* d_row_dalpha,
-                         double* d_row_dsigma, void* stream) {
-  if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: null argument");
+static int glm_launch_common(stan_cuda_data_t d, uint32_t flags, LaunchIO io, void* stream) {
   SC_CUDA(cudaSetDevice(d->device));
-  LaunchIO io{flags, d_params, d_alpha_vec, d_sigma_vec, d_result, d_row_dalpha, d_row_dsigma};
   if (flags & STAN_CUDA_FUSED_ALLREDUCE) {
     PeerXchg* x = comm_rank_xchg();
     if (!x) return fail(STAN_CUDA_ERR_STATE, "stan_cuda_glm_launch: STAN_CUDA_FUSED_ALLREDUCE without a peer exchange "
@@ -339,6 +335,26 @@ int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_par
     counters().fused_allreduces.fetch_add(1, std::memory_order_relaxed);
   }
   return launch_glm(d, io, &d->ws, static_cast<cudaStream_t>(stream));
+}
+
+int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_params, const double* d_alpha_vec,
+                         const double* d_sigma_vec, double* d_result, double* d_row_dalpha,
+                         double* d_row_dsigma, void* stream) {
+  if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: null argument");
+  if (d->family == STAN_CUDA_ORDERED_LOGISTIC)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: ordered_logistic data goes through stan_cuda_glm_launch_ordered");
+  LaunchIO io{flags, d_params, d_alpha_vec, d_sigma_vec, d_result, d_row_dalpha, d_row_dsigma};
+  return glm_launch_common(d, flags, io, stream);
+}
+
+int stan_cuda_glm_launch_ordered(stan_cuda_data_t d, uint32_t flags, const double* d_params, int ncuts,
+                                 double* d_result, void* stream) {
+  if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_ordered: null argument");
+  if (d->family != STAN_CUDA_ORDERED_LOGISTIC)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_ordered: data block of another family");
+  LaunchIO io{flags, d_params, nullptr, nullptr, d_result, nullptr, nullptr};
+  io.ncuts = ncuts;
+  return glm_launch_common(d, flags, io, stream);
 }
 
 }  // extern "C"

@@ -33,6 +33,7 @@ struct GlmKernelParams {
   double lgamma_sum;
   const double* nb_sums;  // neg_binomial_2_log with a histogram of y: [sum lgamma(y+phi), sum digamma(y+phi)]
   int nb_rowfun;          // neg_binomial_2_log: per-row lgamma/digamma (vector phi or no histogram)
+  int ncuts;              // ordered_logistic: number of cut-points (classes - 1); 0 otherwise
   // low-latency host path: parameters by value, completion flag in mapped host memory
   int inline_n;                        // > 0: read the parameter block from inline_params
   unsigned long long* host_flag;       // non-null: store host_seq there after the result block
@@ -240,6 +241,34 @@ __device__ __forceinline__ RowTerms nb_row_epilogue(double eta, double alpha, do
   return o;
 }
 
+// ordered_logistic_glm_lpmf.hpp:104-171, one row of class c (1 .. ncuts + 1); `cuts` in shared
+// memory.  t0 = log-density of the row, d = d1 - d2 (location derivative), t2 = d1, t3 = d2
+// (the row's contributions to d/dcuts[c-2] and d/dcuts[c-1], :192-200).
+__device__ __forceinline__ double log1m_exp_dev(double a) {  // prim/scal/fun/log1m_exp.hpp:44-54
+  if (a >= 0) return nan("");
+  return a > -0.693147 ? log(-expm1(a)) : log1p(-exp(a));
+}
+__device__ __forceinline__ RowTerms ordered_row_epilogue(double loc, int c, int ncuts, const double* cuts) {
+  RowTerms o;
+  const int ncls = ncuts + 1;
+  const double inf = __longlong_as_double(0x7ff0000000000000LL);
+  const double cy1 = c != ncls ? cuts[c - 1] : inf;                                   // :104-115
+  const double cy2 = c != 1 ? cuts[c - 2] : -inf;
+  const double cut2 = loc - cy2, cut1 = loc - cy1;                                    // :124-125
+  const double m1 = (cut1 > 0.0 ? -cut1 : 0.0) - log1p(exp(-fabs(cut1)));            // :128-129
+  const double m2 = (cut2 <= 0.0 ? cut2 : 0.0) - log1p(exp(-fabs(cut2)));            // :130-131
+  o.t0 = c == 1 ? m1 : (c == ncls ? m2 : m2 + log1m_exp_dev(cut1 - cut2) + m1);       // :137-144
+  const double ecd = exp(cy2 - cy1);                                                  // :164
+  const double s2 = cut2 > 0 ? exp(-cut2) / (1 + exp(-cut2)) : 1 / (1 + exp(cut2));   // :165-167
+  const double s1 = cut1 > 0 ? exp(-cut1) / (1 + exp(-cut1)) : 1 / (1 + exp(cut1));   // :168-171
+  const double d1 = s2 - ecd / (ecd - 1);
+  const double d2 = 1 / (1 - ecd) - s1;
+  o.d = d1 - d2;                                                                      // :173
+  o.t2 = d1;
+  o.t3 = d2;
+  return o;
+}
+
 template <int FAMILY>
 __device__ __forceinline__ RowTerms row_epilogue(double eta, double alpha, double yv, double inv_sigma) {
   RowTerms o;
@@ -346,6 +375,9 @@ __device__ __forceinline__ void finish_reduction(const GlmKernelParams& p, int t
       if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;  // :102-108
       if (p.flags & STAN_CUDA_LP_MAIN) lp += A0;             // :109-112
       witness = A1;  // poisson_log_glm_lpmf.hpp:97 tests sum(theta_derivative)
+    } else if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
+      if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
+      witness = A2;  // ordered_logistic_glm_lpmf.hpp:119 tests sum(location)
     } else if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
       // neg_binomial_2_log_glm_lpmf.hpp:130-153, :185-190; A0 already holds the flagged row terms
       const double phi = sigma0;

@@ -344,6 +344,8 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->blocked = 0;
   p->nb_sums = nullptr;
   p->nb_rowfun = 1;
+  p->ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
+  if (p->ncuts < 0 || p->ncuts > kMaxCuts) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
   p->x = d->x;
   p->y = d->y;
   p->n = d->n;
@@ -366,9 +368,10 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->inline_n = 0;
   p->host_flag = io.host_flag;
   p->host_seq = io.host_seq;
-  if (io.h_params_inline && t.kpad + 2 <= kInlineParams) {
-    p->inline_n = t.kpad + 2;
-    for (int i = 0; i < t.kpad + 2; ++i) p->inline_params[i] = io.h_params_inline[i];
+  const int np = t.kpad + 2 + p->ncuts;
+  if (io.h_params_inline && np <= kInlineParams) {
+    p->inline_n = np;
+    for (int i = 0; i < np; ++i) p->inline_params[i] = io.h_params_inline[i];
   } else if (!io.d_params) {
     return fail(STAN_CUDA_ERR_ARG, "launch_glm: no parameter block");
   }
@@ -378,7 +381,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->xchg_local = nullptr;
   for (int q = 0; q < kXchgMaxWorld; ++q) p->xchg_peers[q] = nullptr;
   if (io.xchg && io.xchg->world > 1) {
-    if (t.kpad + 4 > kXchgCols) return fail(STAN_CUDA_ERR_ARG, "launch_glm: result block exceeds the exchange slot");
+    if (t.kpad + 4 + p->ncuts > kXchgCols) return fail(STAN_CUDA_ERR_ARG, "launch_glm: result block exceeds the exchange slot");
     p->xchg_world = io.xchg->world;
     p->xchg_rank = io.xchg->rank;
     p->xchg_local = io.xchg->local;
@@ -393,8 +396,8 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
   if (t.layout == kLayoutWarp) return launch_glm_warp(d, io, ws, stream);
-  if (d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG)
-    return fail(STAN_CUDA_ERR_ARG, "launch_glm: neg_binomial_2_log runs on the warp kernel only");
+  if (d->family >= STAN_CUDA_NEG_BINOMIAL_2_LOG)
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: neg_binomial_2_log and ordered_logistic run on the warp kernel only");
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
   const int sms = sm_count(d->device);
   int ctas_per_sm = tuning().ctas_per_sm;

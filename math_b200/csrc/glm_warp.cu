@@ -43,9 +43,12 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   const int rl = lane / C;
 
   unsigned char* stage0 = smem;
-  double* red = reinterpret_cast<double*>(smem + size_t(p.stages) * p.stage_bytes);  // [WARPS][kpad + 4]
-  double* part = red + size_t(kWarpConsumers) * (kpad + 4);                          // [8]
-  uint64_t* full = reinterpret_cast<uint64_t*>(part + 8);                            // [stages]
+  const int ncuts = FAMILY == STAN_CUDA_ORDERED_LOGISTIC ? p.ncuts : 0;
+  const int cols = kpad + 4 + ncuts;  // width of a partial: [lp, sum d, a2, a3, dbeta(kpad), dcuts(ncuts)]
+  double* red = reinterpret_cast<double*>(smem + size_t(p.stages) * p.stage_bytes);  // [WARPS][cols]
+  double* part = red + size_t(kWarpConsumers) * cols;                                // [8]
+  double* cuts_s = part + 8;                                                         // [ncuts]
+  uint64_t* full = reinterpret_cast<uint64_t*>(cuts_s + ncuts);                      // [stages]
   int* arrived = reinterpret_cast<int*>(full + p.stages);                            // [stages]
   __shared__ int s_flag;
 
@@ -69,6 +72,11 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
       arrived[s] = 0;
     }
     mbar_fence_init();
+  }
+  if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
+    // cut-points into shared memory; the per-warp bins of d/dcuts (tail of each warp's row of `red`) start at zero
+    for (int j = tid; j < ncuts; j += NT) cuts_s[j] = kernel_param(p, kpad + 2 + j);
+    for (int j = tid; j < kWarpConsumers * ncuts; j += NT) red[size_t(j / ncuts) * cols + kpad + 4 + j % ncuts] = 0.0;
   }
   __syncthreads();
 
@@ -160,13 +168,33 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
       }
     }
     RowTerms o;
-    if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
+    if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
+      const int c = valid ? int(yv) : 1;  // 1 <= c <= ncuts + 1 was checked from the range of y cached at fill
+      o = ordered_row_epilogue(eta, c, ncuts, cuts_s);
+      if (valid && cg == 0) {
+        a0 += o.t0;
+        a1 += o.d;
+        a2 += eta;  // ordered_logistic_glm_lpmf.hpp:119: finiteness of sum(location)
+      }
+      if ((p.flags & STAN_CUDA_NEED_DCUTS) && ncuts > 0) {
+        // d/dcuts (:192-200): one owner lane per row adds into this warp's bins, rows in order, so the
+        // sum is the same on every run (no floating-point atomics)
+        double* bins = red + size_t(warp) * cols + kpad + 4;
+        for (int r = 0; r < rpw; ++r) {
+          if (rl == r && cg == 0 && valid) {
+            if (c != ncuts + 1) bins[c - 1] += o.t3;
+            if (c != 1) bins[c - 2] -= o.t2;
+          }
+          __syncwarp();
+        }
+      }
+    } else if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
       o = nb_row_epilogue(eta, alpha, yv, sigma_row, log_sigma_row, p.flags, p.nb_rowfun != 0);
     } else {
       o = row_epilogue<FAMILY>(eta, alpha, yv, inv_sigma);
     }
     const double d = valid ? o.d : 0.0;
-    if (valid && cg == 0) {
+    if (FAMILY != STAN_CUDA_ORDERED_LOGISTIC && valid && cg == 0) {
       a0 += o.t0;
       a1 += o.d;
       a2 += o.t2;
@@ -203,7 +231,6 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
       a3 += o3;
     }
   }
-  const int cols = kpad + 4;
   double* myred = red + size_t(warp) * cols;
   if (rl == 0) {  // lanes 0 .. C-1 hold the sums of column group cg = lane
 #pragma unroll
@@ -233,10 +260,10 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
 // =============================================================================================
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-static size_t warp_smem_bytes(const Tiling& t, int stages, size_t* stage_bytes_out) {
+static size_t warp_smem_bytes(const Tiling& t, int stages, int ncuts, size_t* stage_bytes_out) {
   const size_t stage = align_up(t.tile_bytes() + size_t(t.R) * sizeof(double), 128);
   if (stage_bytes_out) *stage_bytes_out = stage;
-  const size_t fixed = (size_t(kWarpConsumers) * (t.kpad + 4) + 8) * sizeof(double) + size_t(stages) * (sizeof(uint64_t) + sizeof(int)) + 8;
+  const size_t fixed = (size_t(kWarpConsumers) * (t.kpad + 4 + ncuts) + 8 + ncuts) * sizeof(double) + size_t(stages) * (sizeof(uint64_t) + sizeof(int)) + 8;
   return size_t(stages) * stage + fixed;
 }
 
@@ -312,14 +339,18 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   int ctas_per_sm = tuning().ctas_per_sm;
   if (ctas_per_sm <= 0 || ctas_per_sm > 2) ctas_per_sm = 2;
   const size_t budget = (size_t(228) * 1024) / ctas_per_sm - 1024 - 64;
+  const int ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
+  if (ncuts < 0 || ncuts > kMaxCuts)
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
+  const size_t cols = size_t(t.kpad) + 4 + ncuts;
   int stages = tuning().stages;
   size_t stage_bytes = 0;
   if (stages <= 0) {
     stages = 6;
-    while (stages > 2 && warp_smem_bytes(t, stages, nullptr) > budget) --stages;
+    while (stages > 2 && warp_smem_bytes(t, stages, ncuts, nullptr) > budget) --stages;
   }
-  size_t smem = warp_smem_bytes(t, stages, &stage_bytes);
-  while (stages > 1 && smem > size_t(227) * 1024) smem = warp_smem_bytes(t, --stages, &stage_bytes);
+  size_t smem = warp_smem_bytes(t, stages, ncuts, &stage_bytes);
+  while (stages > 1 && smem > size_t(227) * 1024) smem = warp_smem_bytes(t, --stages, ncuts, &stage_bytes);
   if (smem > size_t(227) * 1024) return fail(STAN_CUDA_ERR_ARG, "launch_glm: tile does not fit shared memory");
 
   int64_t grid64 = int64_t(sms) * ctas_per_sm;
@@ -329,7 +360,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   while (group_size * group_size < grid) ++group_size;
   const int ngroups = (grid + group_size - 1) / group_size;
   if (ngroups > 60) return fail(STAN_CUDA_ERR_ARG, "launch_glm: grid too large for the ticket block");
-  SC_TRY(workspace_reserve(ws, d->device, size_t(grid + ngroups) * (t.kpad + 4) + 2));
+  SC_TRY(workspace_reserve(ws, d->device, size_t(grid + ngroups) * cols + 2));
 
   GlmKernelParams p;
   SC_TRY(fill_kernel_params(d, io, ws, &p));
@@ -352,6 +383,9 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
       SC_TRY(prepare_neg_binomial(d, io, ws, &p, stream));
       return rowio ? launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, true>(p, grid, smem, stream)
                    : launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, false>(p, grid, smem, stream);
+    case STAN_CUDA_ORDERED_LOGISTIC:
+      if (rowio) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic has no per-row operands");
+      return launch_warp_inst<STAN_CUDA_ORDERED_LOGISTIC, false>(p, grid, smem, stream);
   }
   return fail(STAN_CUDA_ERR_ARG, "launch_glm: unknown family");
 }

@@ -247,6 +247,81 @@ def neg_binomial_2_log_glm_lpmf(y, x, alpha, beta, phi, propto=False):
     return _glm("neg_binomial_2_log_glm_lpmf", _abi.NEG_BINOMIAL_2_LOG, y, x, alpha, beta, phi, propto)
 
 
+def ordered_logistic_glm_eval(y, x, beta, cuts, flags):
+    """Raw C-ABI call for family ORDERED_LOGISTIC: dict with rc, lp, dbeta, dcuts."""
+    x, row_major, ldx = _prep_x(x)
+    n, k = x.shape
+    y = np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+    beta = _f64(beta)
+    cuts = _f64(cuts) if np.size(cuts) else np.zeros(0)
+    a = _abi.GlmArgs()
+    lp, dbeta, dcuts, aux = np.zeros(1), np.zeros(max(k, 1)), np.zeros(max(cuts.size, 1)), np.zeros(4)
+    a.family, a.flags, a.n, a.k = _abi.ORDERED_LOGISTIC, flags, n, k
+    a.x, a.ldx, a.x_row_major = x.ctypes.data, ldx, row_major
+    a.y, a.y_is_double = y.ctypes.data, 0
+    a.alpha, a.alpha_len, a.beta = None, 1, beta.ctypes.data
+    a.cuts, a.cuts_len, a.dcuts = cuts.ctypes.data, cuts.size, dcuts.ctypes.data
+    a.lp, a.dbeta, a.aux = lp.ctypes.data, dbeta.ctypes.data, aux.ctypes.data
+    rc = check(lib().stan_cuda_glm_eval(C.byref(a)))
+    return {"rc": rc, "lp": float(lp[0]), "dbeta": dbeta[:k].copy(), "dcuts": dcuts[:cuts.size].copy(), "aux": aux,
+            "_keep": (x, y)}
+
+
+def ordered_logistic_glm_lpmf(y, x, beta, cuts, propto=False, beta_var=True, cuts_var=True):
+    """stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:46-52; grads: beta, cuts.
+    Checks in the reference's order (:71-86); check_bounded(y, 1, N_classes) is answered by the
+    device from the range of y cached at fill."""
+    function = "ordered_logistic_glm_lpmf"
+    xa = np.asarray(x, dtype=np.float64)
+    if xa.ndim != 2:
+        raise ValueError("%s: x must be a matrix" % function)
+    n, k = xa.shape
+    ya = np.atleast_1d(np.asarray(y))
+    be = _f64(beta)
+    cu = _f64(cuts) if np.size(cuts) else np.zeros(0)
+    n_classes = cu.size + 1
+    if ya.size != n:
+        raise ValueError("%s: Vector of dependent variables has dimension = %d, expecting dimension = %d"
+                         % (function, ya.size, n))
+    if be.size != k:
+        raise ValueError("%s: Weight vector has dimension = %d, expecting dimension = %d" % (function, be.size, k))
+
+    def y_error():
+        return DomainError("%s: Vector of dependent variables must be in the interval [1, %d]" % (function, n_classes))
+
+    def cuts_error():
+        if cu.size > 1 and not np.all(cu[1:] > cu[:-1]):   # check_ordered: strictly ascending, NaN fails
+            return DomainError("%s: Cut-points is not a valid ordered vector" % function)
+        if cu.size and not (np.isfinite(cu[-1]) and np.isfinite(cu[0])):
+            return DomainError("%s: cut-point is not finite" % function)
+        return None
+
+    ce = cuts_error()
+    nothing_to_do = n == 0 or cu.size == 0 or (propto and not (beta_var or cuts_var))
+    if ce is not None or nothing_to_do:
+        # error path or early return (:88-92): nothing goes to the device, the outcome check runs here
+        if n and (ya.min() < 1 or ya.max() > n_classes):
+            raise y_error()
+        if ce is not None:
+            raise ce
+        return 0.0, {}
+    flags = _abi.LP_MAIN | (_abi.NEED_DBETA if beta_var else 0) | (_abi.NEED_DCUTS if cuts_var else 0)
+    r = ordered_logistic_glm_eval(ya, xa, be, cu, flags)
+    if r["rc"] == _abi.BAD_OUTCOME:
+        raise y_error()
+    if r["rc"] == _abi.NONFINITE:      # :119-122
+        if not np.all(np.isfinite(be)):
+            raise DomainError("%s: Weight vector is not finite" % function)
+        if not np.all(np.isfinite(xa)):
+            raise DomainError("%s: Matrix of independent variables is not finite" % function)
+    grads = {}
+    if beta_var:
+        grads["beta"] = r["dbeta"]
+    if cuts_var:
+        grads["cuts"] = r["dcuts"]
+    return r["lp"], grads
+
+
 def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
     """normal_lpdf(y | mu, sigma) with mu and sigma as the differentiated operands."""
     function = "normal_lpdf"

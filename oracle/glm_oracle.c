@@ -212,9 +212,51 @@ static int neg_binomial_2_log_glm(const stan_cuda_glm_args* a, double* d) {
   return isfinite(witness) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;                       /* :120 check_finite(theta) */
 }
 
+/* stan/math/prim/scal/fun/log1m_exp.hpp:44-54 */
+static double oracle_log1m_exp(double a) {
+  if (a >= 0) return NAN;
+  if (a > -0.693147) return log(-expm1(a));
+  return log1p(-exp(a));
+}
+
+/* ordered_logistic_glm_lpmf.hpp:93-199: location = x*beta (no intercept); d = d1 - d2 */
+static int ordered_logistic_glm(const stan_cuda_glm_args* a, double* d) {
+  const int64_t ncls = a->cuts_len + 1;
+  double logp = 0.0, sum_d = 0.0, witness = 0.0;
+  double* loc = linear_predictor(a);
+  if (!loc) return STAN_CUDA_ERR_ARG;
+  const int want_dcuts = (a->flags & STAN_CUDA_NEED_DCUTS) && a->dcuts;
+  if (want_dcuts) for (int64_t j = 0; j < a->cuts_len; ++j) a->dcuts[j] = 0.0;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const int64_t c = (int64_t)y_at(a, i);
+    const double cy1 = c != ncls ? a->cuts[c - 1] : INFINITY;                       /* :104-115 */
+    const double cy2 = c != 1 ? a->cuts[c - 2] : -INFINITY;
+    const double cut2 = loc[i] - cy2, cut1 = loc[i] - cy1;                          /* :124-125 */
+    const double m1 = (cut1 > 0.0 ? -cut1 : 0.0) - log1p(exp(-fabs(cut1)));        /* :128-129 */
+    const double m2 = (cut2 <= 0.0 ? cut2 : 0.0) - log1p(exp(-fabs(cut2)));        /* :130-131 */
+    if (c == 1) logp += m1;                                                         /* :137-144 */
+    else if (c == ncls) logp += m2;
+    else logp += m2 + oracle_log1m_exp(cut1 - cut2) + m1;
+    const double e1 = exp(-cut1), e2 = exp(-cut2), ecd = exp(cy2 - cy1);            /* :162-164 */
+    const double d1 = (cut2 > 0 ? e2 / (1 + e2) : 1 / (1 + exp(cut2))) - ecd / (ecd - 1);  /* :165-167 */
+    const double d2 = 1 / (1 - ecd) - (cut1 > 0 ? e1 / (1 + e1) : 1 / (1 + exp(cut1)));    /* :168-171 */
+    d[i] = d1 - d2;                                                                 /* :173 */
+    sum_d += d[i];
+    if (want_dcuts) {                                                               /* :192-200 */
+      if (c != ncls) a->dcuts[c - 1] += d2;
+      if (c != 1) a->dcuts[c - 2] -= d1;
+    }
+    witness += loc[i];                                                              /* :119 */
+  }
+  free(loc);
+  if (a->lp) *a->lp = (a->flags & STAN_CUDA_LP_MAIN) ? logp : 0.0;
+  if (a->aux) { a->aux[0] = sum_d; a->aux[1] = witness; a->aux[2] = 0; a->aux[3] = 0; }
+  return isfinite(witness) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
 int oracle_glm_eval(const stan_cuda_glm_args* a) {
   if (!a || a->n < 0 || a->k < 0) return STAN_CUDA_ERR_ARG;
-  if (a->alpha_len != 1 && a->alpha_len != a->n) return STAN_CUDA_ERR_ARG;
+  if (a->family != STAN_CUDA_ORDERED_LOGISTIC && a->alpha_len != 1 && a->alpha_len != a->n) return STAN_CUDA_ERR_ARG;
   double* d = (double*)calloc((size_t)(a->n > 0 ? a->n : 1), sizeof(double));
   if (!d) return STAN_CUDA_ERR_ARG;
   int rc;
@@ -228,6 +270,10 @@ int oracle_glm_eval(const stan_cuda_glm_args* a) {
     case STAN_CUDA_NEG_BINOMIAL_2_LOG:
       if (a->sigma_len != 1 && a->sigma_len != a->n) { free(d); return STAN_CUDA_ERR_ARG; }
       rc = neg_binomial_2_log_glm(a, d);
+      break;
+    case STAN_CUDA_ORDERED_LOGISTIC:
+      if (a->cuts_len < 0 || (a->cuts_len > 0 && !a->cuts)) { free(d); return STAN_CUDA_ERR_ARG; }
+      rc = ordered_logistic_glm(a, d);
       break;
     default: free(d); return STAN_CUDA_ERR_ARG;
   }

@@ -55,6 +55,9 @@ def ref_lib():
         lib.stanref_glm.restype = i
         lib.stanref_glm.argtypes = [i, i, l, l, dp, vp, dp, l, dp, dp, l, i, dp, dp, dp, dp, dp, dp,
                                     C.c_char_p, i]
+        if hasattr(lib, "stanref_ordered_logistic_glm"):
+            lib.stanref_ordered_logistic_glm.restype = i
+            lib.stanref_ordered_logistic_glm.argtypes = [i, l, l, dp, vp, dp, dp, l, dp, dp, dp, dp, C.c_char_p, i]
         lib.stanref_glm_value.restype = i
         lib.stanref_glm_value.argtypes = [i, i, l, l, dp, vp, dp, l, dp, dp, l, dp, C.c_char_p, i]
         lib.stanref_normal_lpdf.restype = i
@@ -100,7 +103,7 @@ def prep_glm(family, x, y, alpha, beta, sigma=None):
     return fam, x, y, alpha, beta, sigma
 
 
-def glm_args(fam, x, y, alpha, beta, sigma, flags, need_dy=False):
+def glm_args(fam, x, y, alpha, beta, sigma, flags, need_dy=False, cuts=None):
     """Build a GlmArgs block + its output arrays (kept alive in the returned dict)."""
     n, k = x.shape
     out = {
@@ -117,7 +120,10 @@ def glm_args(fam, x, y, alpha, beta, sigma, flags, need_dy=False):
     a.sigma, a.sigma_len = (_ptr(sigma), sigma.size) if sigma is not None else (None, 0)
     a.lp, a.dbeta, a.dalpha = out["lp"].ctypes.data, out["dbeta"].ctypes.data, out["dalpha"].ctypes.data
     a.dsigma, a.dy, a.aux = out["dsigma"].ctypes.data, _ptr(out["dy"]), out["aux"].ctypes.data
-    out["_keep"] = (x, y, alpha, beta, sigma)
+    if cuts is not None:
+        out["dcuts"] = np.zeros(max(cuts.size, 1))
+        a.cuts, a.cuts_len, a.dcuts = cuts.ctypes.data, cuts.size, out["dcuts"].ctypes.data
+    out["_keep"] = (x, y, alpha, beta, sigma, cuts)
     return a, out
 
 
@@ -159,6 +165,21 @@ def oracle_glm(family, x, y, alpha, beta, sigma=None, propto=False, need_dy=Fals
     return _finish_glm(rc, out, fam, x.shape[0], x.shape[1], alpha, sigma)
 
 
+def ordered_flags(propto=False):
+    """every summand depends on beta / cuts: propto changes nothing when they are vars
+    (ordered_logistic_glm_lpmf.hpp:93-94)"""
+    return _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+
+
+def oracle_ordered_logistic_glm(x, y, beta, cuts, propto=False, flags=None):
+    fam, x, y, alpha, beta, _ = prep_glm(_abi.ORDERED_LOGISTIC, x, y, 0.0, beta, None)
+    cuts = _f64(cuts) if np.size(cuts) else np.zeros(0)
+    a, out = glm_args(fam, x, y, alpha, beta, None, ordered_flags(propto) if flags is None else flags, cuts=cuts)
+    rc = oracle_lib().oracle_glm_eval(C.byref(a))
+    return {"rc": rc, "lp": float(out["lp"][0]), "dbeta": out["dbeta"][:x.shape[1]].copy(),
+            "dcuts": out["dcuts"][:cuts.size].copy(), "aux": out["aux"].copy()}
+
+
 class RefError(Exception):
     def __init__(self, rc, msg):
         super().__init__(msg)
@@ -189,6 +210,21 @@ def ref_glm(family, x, y, alpha, beta, sigma=None, propto=False, need_dy=False):
     if need_dy:
         res["dy"] = dy[:n].copy()
     return res
+
+
+def ref_ordered_logistic_glm(x, y, beta, cuts, propto=False):
+    fam, x, y, alpha, beta, _ = prep_glm(_abi.ORDERED_LOGISTIC, x, y, 0.0, beta, None)
+    cuts = _f64(cuts) if np.size(cuts) else np.zeros(0)
+    n, k = x.shape
+    lp, dbeta, dcuts, secs = np.zeros(1), np.zeros(max(k, 1)), np.zeros(max(cuts.size, 1)), np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_ordered_logistic_glm(int(propto), n, k, x.ctypes.data, y.ctypes.data, beta.ctypes.data,
+                                                cuts.ctypes.data, cuts.size, lp.ctypes.data, dbeta.ctypes.data,
+                                                dcuts.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return {"rc": 0, "lp": float(lp[0]), "dbeta": dbeta[:k].copy(), "dcuts": dcuts[:cuts.size].copy(),
+            "seconds": float(secs[0])}
 
 
 def ref_glm_value(family, x, y, alpha, beta, sigma=None, propto=False):

@@ -15,6 +15,7 @@
 //   normal_id_glm_lpdf        stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:49-174
 //   normal_lpdf               stan/math/prim/scal/prob/normal_lpdf.hpp:36-112
 //   neg_binomial_2_log_glm_lpmf stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:60-197
+//   ordered_logistic_glm_lpmf stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:46-222
 //   map_rect                  stan/math/prim/mat/functor/map_rect.hpp:120-177
 #include <stan/math.hpp>
 
@@ -149,6 +150,29 @@ int stanref_glm(int family, int propto, long n, long k, const double* x,
           if (sv) read_adj(sigma_vec, dsigma); else dsigma[0] = s0.adj();
         }
         if (dy && y_is_var) read_adj(y_v, dy);
+      },
+      err, errlen);
+}
+
+// ordered_logistic_glm_lpmf(y, x, beta, cuts) with var beta and cuts: value + gradient.
+int stanref_ordered_logistic_glm(int propto, long n, long k, const double* x, const int* y,
+                                 const double* beta, const double* cuts, long ncuts, double* lp,
+                                 double* dbeta, double* dcuts, double* seconds, char* err, int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d xm = Eigen::Map<const matrix_d>(x, n, k);
+        std::vector<int> yi(y, y + n);
+        vector_v beta_v = make_vars(beta, k);
+        vector_v cuts_v = make_vars(cuts, ncuts);
+        auto t0 = std::chrono::steady_clock::now();
+        var res = propto ? stan::math::ordered_logistic_glm_lpmf<true>(yi, xm, beta_v, cuts_v)
+                         : stan::math::ordered_logistic_glm_lpmf<false>(yi, xm, beta_v, cuts_v);
+        res.grad();
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        if (lp) *lp = res.val();
+        read_adj(beta_v, dbeta);
+        read_adj(cuts_v, dcuts);
       },
       err, errlen);
 }

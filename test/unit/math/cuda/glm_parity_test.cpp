@@ -179,6 +179,33 @@ TEST(CudaGlmVariants, vector_alpha_vector_sigma_var_y) {
   stan::math::recover_memory();
 }
 
+TEST(CudaGlmVariants, ordered_logistic) {
+  using stan::math::ordered_logistic_glm_lpmf;
+  using stan::math::ordered_logistic_glm_lpmf_reference_cpu;
+  Problem p = make_problem(5003, 37, 11);
+  vector_v beta = to_v(p.beta);
+  VectorXd cuts_d(4);
+  cuts_d << -0.8, -0.1, 0.4, 1.3;
+  vector_v cuts = to_v(cuts_d);
+  std::vector<int> y(p.y_pois.size());
+  for (size_t i = 0; i < y.size(); ++i) y[i] = 1 + (p.y_pois[i] + static_cast<int>(i)) % 5;
+  STAN_CUDA_PARITY("ordered_logistic", ordered_logistic_glm_lpmf(y, p.x, beta, cuts),
+                   ordered_logistic_glm_lpmf_reference_cpu(y, p.x, beta, cuts), adj(beta), adj(cuts));
+  STAN_CUDA_PARITY("ordered_logistic propto, data cuts", ordered_logistic_glm_lpmf<true>(y, p.x, beta, cuts_d),
+                   ordered_logistic_glm_lpmf_reference_cpu<true>(y, p.x, beta, cuts_d), adj(beta));
+  STAN_CUDA_PARITY("ordered_logistic data beta", ordered_logistic_glm_lpmf(y, p.x, p.beta, cuts),
+                   ordered_logistic_glm_lpmf_reference_cpu(y, p.x, p.beta, cuts), adj(cuts));
+  EXPECT_NEAR(ordered_logistic_glm_lpmf(y, p.x, p.beta, cuts_d),
+              ordered_logistic_glm_lpmf_reference_cpu(y, p.x, p.beta, cuts_d), 1e-8);
+  EXPECT_EQ(ordered_logistic_glm_lpmf<true>(y, p.x, p.beta, cuts_d), 0.0);
+  // out-of-range class: same exception as the reference, thrown from the device's cached range of y
+  std::vector<int> y_high = y, y_low = y;
+  y_high[17] = 6;
+  y_low[17] = 0;
+  EXPECT_THROW(ordered_logistic_glm_lpmf(y_high, p.x, beta, cuts), std::domain_error);
+  EXPECT_THROW(ordered_logistic_glm_lpmf(y_low, p.x, beta, cuts), std::domain_error);
+}
+
 TEST(CudaGlmVariants, zero_copy_data_view) {
   Problem p = make_problem(4001, 37, 9);
   vector_v beta = to_v(p.beta);

@@ -135,7 +135,38 @@ for n, k, tag in ((153, 71, "nbbig"), (600, 128, "nbwide"), (1000, 1, "nbk1")):
         add_glm("nb_big_valpha_vphi_propto", "neg_binomial_2_log", x, yc, av, beta, pv, propto=True, xkey=tag)
         add_glm("nb_big_counts", "neg_binomial_2_log", x, rng2.integers(0, 200, n), 0.3, beta, [1.5], xkey=tag)
 
+# ordered_logistic_glm (own key space "ord/"): the fixed fixture of
+# test/unit/math/rev/mat/prob/ordered_logistic_glm_lpmf_test.cpp:33-47 (y = {1,4,3,3,2}, cuts = (0.9, 1.1, 7),
+# beta = (1.1, 0.4), x = [1 2; 3 4; 5 6; 7 8; 9 0]), a single-cut case, and random cases up to 10 classes (:293-331)
+ord_names = []
+
+
+def add_ord(name, x, y, beta, cuts, propto=False):
+    r = L.ref_ordered_logistic_glm(x, y, beta, cuts, propto=propto)
+    p = "ord/%s/" % name
+    out[p + "x"], out[p + "y"] = np.asarray(x, float), np.asarray(y, np.int32)
+    out[p + "beta"], out[p + "cuts"] = np.atleast_1d(np.asarray(beta, float)), np.atleast_1d(np.asarray(cuts, float))
+    out[p + "propto"] = np.array(int(propto))
+    out[p + "lp"], out[p + "dbeta"], out[p + "dcuts"] = np.array(r["lp"]), r["dbeta"], r["dcuts"]
+    ord_names.append(name)
+
+
+rng3 = np.random.default_rng(20191106)
+XO = np.array([[1, 2], [3, 4], [5, 6], [7, 8], [9, 0]], float)
+add_ord("fixture", XO, [1, 4, 3, 3, 2], [1.1, 0.4], [0.9, 1.1, 7])
+add_ord("fixture_propto", XO, [1, 4, 3, 3, 2], [1.1, 0.4], [0.9, 1.1, 7], propto=True)
+add_ord("two_classes", XO, [1, 2, 2, 1, 2], [0.11, -0.4], [0.3])
+for n, k, c, tag in ((153, 71, 4, "big"), (600, 128, 10, "wide"), (1000, 1, 3, "k1"), (777, 33, 40, "many")):
+    x = rng3.standard_normal((n, k))
+    beta = rng3.standard_normal(k) * (1.5 / np.sqrt(k))
+    cuts = np.sort(rng3.standard_normal(c - 1) * 1.5)
+    add_ord("rand_" + tag, x, rng3.integers(1, c + 1, n), beta, cuts)
+# far tails: locations +-40 from the cut-points (the branches of :128-131 and :165-171)
+x = rng3.standard_normal((64, 2)) * 30
+add_ord("tails", x, rng3.integers(1, 4, 64), [1.0, -1.0], [-1.0, 2.0])
+
 out["glm_cases"] = np.array(names)
+out["ord_cases"] = np.array(ord_names)
 out["normal_cases"] = np.array(nl)
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "glm_golden.npz")
 np.savez_compressed(path, **out)

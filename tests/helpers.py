@@ -77,3 +77,29 @@ def synth_glm(family, n, k, seed, dtype_y=None):
     beta = beta_true + 0.02 * rng.standard_normal(k)
     return {"family": fam, "x": x, "y": y, "alpha": np.array([0.3]), "beta": beta,
             "sigma": np.array([1.0]) if fam == _abi.NORMAL_ID else (np.array([2.5]) if fam == _abi.NEG_BINOMIAL_2_LOG else None)}
+
+
+def ord_case(golden, name):
+    p = "ord/%s/" % name
+    c = {k: golden[p + k] for k in ("x", "y", "beta", "cuts", "dbeta", "dcuts")}
+    c["lp"], c["propto"] = float(golden[p + "lp"]), bool(golden[p + "propto"])
+    return c
+
+
+def check_ord_result(r, c, what, rtol=RTOL):
+    assert_close(r["lp"], c["lp"], what + " lp", rtol)
+    assert_close(r["dbeta"], c["dbeta"], what + " dbeta", rtol)
+    assert_close(r["dcuts"], c["dcuts"], what + " dcuts", rtol)
+
+
+def synth_ordered(n, k, n_classes, seed):
+    """Ordinal outcomes drawn from the model at (beta_true, cuts); evaluated at a perturbed beta."""
+    rng = np.random.default_rng(seed)
+    x = np.asfortranarray(rng.standard_normal((n, k)))
+    beta_true = rng.standard_normal(k) * (1.0 / np.sqrt(k))
+    cuts = np.sort(rng.standard_normal(n_classes - 1) * 1.2)
+    if cuts.size > 1:
+        cuts += np.arange(cuts.size) * 0.05   # strictly ascending
+    lat = x @ beta_true + rng.logistic(size=n)
+    y = (1 + np.searchsorted(cuts, lat)).astype(np.int32)
+    return {"x": x, "y": y, "beta": beta_true + 0.05 * rng.standard_normal(k), "cuts": cuts}

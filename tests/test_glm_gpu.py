@@ -5,7 +5,8 @@ import numpy as np
 import pytest
 
 from math_b200 import _abi
-from tests.helpers import RTOL, assert_close, check_glm_result, glm_case, normal_case, synth_glm
+from tests.helpers import (RTOL, assert_close, check_glm_result, check_ord_result, glm_case, normal_case, ord_case,
+                           synth_glm, synth_ordered)
 
 pytestmark = pytest.mark.gpu
 
@@ -45,6 +46,70 @@ def test_golden_glm_cases(glm, golden):
         r = run_case(glm, c)
         assert r["rc"] == 0, name
         check_glm_result(r, c, "cuda vs golden " + str(name))
+
+
+def test_golden_ordered_logistic_cases(glm, golden):
+    for name in golden["ord_cases"]:
+        c = ord_case(golden, str(name))
+        flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+        r = glm.ordered_logistic_glm_eval(c["y"], c["x"], c["beta"], c["cuts"], flags)
+        assert r["rc"] == 0, name
+        check_ord_result(r, c, "cuda vs golden ord " + str(name))
+        lp, g = glm.ordered_logistic_glm_lpmf(c["y"], c["x"], c["beta"], c["cuts"], propto=c["propto"])
+        assert lp == r["lp"] and np.array_equal(g["cuts"], r["dcuts"]) and np.array_equal(g["beta"], r["dbeta"])
+
+
+ORD_SHAPES = [(1, 1, 2), (5, 2, 3), (33, 7, 1), (1000, 16, 4), (4097, 33, 7), (100000, 32, 5), (30011, 128, 10),
+              (9000, 256, 3), (2100, 500, 6), (50000, 8, 200), (3000, 40, 257)]
+
+
+@pytest.mark.parametrize("n,k,c", ORD_SHAPES)
+def test_ordered_logistic_against_oracle(glm, L, n, k, c):
+    s = synth_ordered(n, k, c, seed=11 * n + k + c)
+    flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+    ref = L.oracle_ordered_logistic_glm(s["x"], s["y"], s["beta"], s["cuts"])
+    got = glm.ordered_logistic_glm_eval(s["y"], s["x"], s["beta"], s["cuts"], flags)
+    assert got["rc"] == ref["rc"] == 0
+    check_ord_result(got, ref, "ordered %dx%d C=%d" % (n, k, c))
+    again = glm.ordered_logistic_glm_eval(s["y"], s["x"], s["beta"], s["cuts"], flags)
+    assert again["lp"] == got["lp"] and np.array_equal(again["dcuts"], got["dcuts"])   # fixed summation order
+    # value only / one edge constant: the other partials are left alone
+    only = glm.ordered_logistic_glm_eval(s["y"], s["x"], s["beta"], s["cuts"], _abi.LP_MAIN | _abi.NEED_DBETA)
+    assert only["lp"] == got["lp"] and np.array_equal(only["dbeta"], got["dbeta"])
+
+
+def test_ordered_logistic_error_contract(glm):
+    """ordered_logistic_glm_lpmf_test.cpp:410-470 (glm_errors)."""
+    x = np.array([[1, 2], [3, 4], [5, 6], [7, 8], [9, 0]], float)
+    y, beta, cuts = [1, 1, 2, 4, 4], [1.1, 0.4], [0.9, 1.1, 7]
+    f = glm.ordered_logistic_glm_lpmf
+    f(y, x, beta, cuts)
+    for bad in ([1, 1, 2, 4, 4, 2],):
+        with pytest.raises(ValueError) as e:
+            f(bad, x, beta, cuts)
+        assert not isinstance(e.value, glm.DomainError)
+    with pytest.raises(ValueError) as e:
+        f(y, x, [1.1, 0.4, 0], cuts)
+    assert not isinstance(e.value, glm.DomainError)
+    for bad_y in ([1, 1, 2, 4, 5], [1, 1, 2, 4, 0]):
+        with pytest.raises(glm.DomainError):
+            f(bad_y, x, beta, cuts)
+    xv = x.copy()
+    xv[3, 1] = np.inf
+    with pytest.raises(glm.DomainError):
+        f(y, xv, beta, cuts)
+    with pytest.raises(glm.DomainError):
+        f(y, x, [1.1, np.inf], cuts)
+    for bad_cuts in ([0.9, 1.1, np.inf], [-np.inf, 1.1, 4], [0, 1.1, 0.5], [0, np.nan, 0.5]):
+        with pytest.raises(glm.DomainError):
+            f(y, x, beta, bad_cuts)
+    # single class / no instances: 0 after the checks (:88-89)
+    assert f([1, 1, 1, 1, 1], x, beta, [])[0] == 0.0
+    assert f([], np.zeros((0, 2)), beta, cuts)[0] == 0.0
+    # more cut-points than the device path holds: loud error, no fallback
+    with pytest.raises(Exception) as e:
+        f([1] * 5, x, beta, np.arange(300.0))
+    assert "256" in str(e.value)
 
 
 def test_golden_normal_cases(glm, golden):

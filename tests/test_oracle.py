@@ -4,7 +4,8 @@ import numpy as np
 import pytest
 
 from oracle import loader as L
-from tests.helpers import assert_close, check_glm_result, glm_case, normal_case, synth_glm
+from tests.helpers import (assert_close, check_glm_result, check_ord_result, glm_case, normal_case, ord_case,
+                           synth_glm, synth_ordered)
 from math_b200 import _abi
 
 
@@ -19,6 +20,15 @@ def test_oracle_glm_matches_golden(golden):
                          propto=c["propto"], need_dy=c["need_dy"])
         assert r["rc"] == 0, name
         check_glm_result(r, c, "oracle vs golden " + str(name), rtol=1e-11)
+
+
+def test_oracle_ordered_logistic_matches_golden(golden):
+    assert len(golden["ord_cases"]) >= 8
+    for name in golden["ord_cases"]:
+        c = ord_case(golden, str(name))
+        r = L.oracle_ordered_logistic_glm(c["x"], c["y"], c["beta"], c["cuts"], propto=c["propto"])
+        assert r["rc"] == 0, name
+        check_ord_result(r, c, "oracle vs golden ord " + str(name), rtol=1e-11)
 
 
 def test_oracle_normal_matches_golden_and_known_answers(golden):
@@ -68,6 +78,15 @@ def test_oracle_vs_compiled_reference(family, n, k):
         ref = L.ref_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"], propto=propto)
         got = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"], propto=propto)
         check_glm_result(got, ref, "%s %dx%d propto=%s" % (family, n, k, propto), rtol=1e-11)
+
+
+@needs_ref
+@pytest.mark.parametrize("n,k,c", [(1, 1, 2), (50, 3, 1), (500, 32, 5), (1200, 130, 12)])
+def test_oracle_ordered_logistic_vs_compiled_reference(n, k, c):
+    s = synth_ordered(n, k, c, seed=n + 7 * k + c)
+    ref = L.ref_ordered_logistic_glm(s["x"], s["y"], s["beta"], s["cuts"])
+    got = L.oracle_ordered_logistic_glm(s["x"], s["y"], s["beta"], s["cuts"])
+    check_ord_result(got, ref, "ordered %dx%d C=%d" % (n, k, c), rtol=1e-11)
 
 
 @needs_ref
