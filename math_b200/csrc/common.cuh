@@ -113,6 +113,7 @@ struct LaunchIO {
   int ncuts = 0;
 };
 constexpr int kMaxCuts = 256;                // ordered_logistic: per-warp bins live in shared memory
+constexpr int kOrdPrivateDoubles = 2048;     // ordered_logistic: ncuts * R up to this -> one private bin row per row slot
 constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sigma)
 
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.

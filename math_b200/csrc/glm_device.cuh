@@ -34,6 +34,7 @@ struct GlmKernelParams {
   const double* nb_sums;  // neg_binomial_2_log with a histogram of y: [sum lgamma(y+phi), sum digamma(y+phi)]
   int nb_rowfun;          // neg_binomial_2_log: per-row lgamma/digamma (vector phi or no histogram)
   int ncuts;              // ordered_logistic: number of cut-points (classes - 1); 0 otherwise
+  int ord_private;        // ordered_logistic: d/dcuts bins private to each row slot of the tile ([ncuts][R] in shared memory)
   // low-latency host path: parameters by value, completion flag in mapped host memory
   int inline_n;                        // > 0: read the parameter block from inline_params
   unsigned long long* host_flag;       // non-null: store host_seq there after the result block
@@ -218,15 +219,31 @@ __device__ __forceinline__ double digamma_pos(double x) {
 // sums from the histogram of y (nb_hist_sums_kernel).  t0 is the row's contribution to the
 // log-density under `flags`; t3 the row's contribution to d/dphi.
 __device__ __forceinline__ RowTerms nb_row_epilogue(double eta, double alpha, double yv, double phi,
-                                                    double log_phi, uint32_t flags, bool rowfun) {
+                                                    double log_phi, double inv_phi, uint32_t flags, bool rowfun,
+                                                    bool ref_order) {
   RowTerms o;
   const double theta = eta + alpha;                                           // :118-119
-  const double lse = theta > log_phi ? theta + log1p(exp(log_phi - theta))    // :122-125
-                                     : log_phi + log1p(exp(theta - log_phi));
+  // one exponential serves the whole row: with u = theta - log phi and e = exp(-|u|),
+  //   logsumexp(theta, log phi) = max + log1p(e)                               (:122-125)
+  //   exp(theta) / (exp(theta) + phi) = sigmoid(u)  = (u > 0 ? 1 : e) / (1 + e)  (:159-162)
+  //   phi / (exp(theta) + phi)        = sigmoid(-u) = (u > 0 ? e : 1) / (1 + e)  (:185-190)
+  const double u = theta - log_phi;
+  const bool pos = u > 0.0;
+  const double e = exp(-fabs(u));
+  const double lse = (pos ? theta : log_phi) + log1p(e);
+  const double inv1pe = 1.0 / (1.0 + e);
   const double ypp = yv + phi;                                                // :127
-  const double te = exp(theta);                                               // :159
-  const double q = ypp / (te + phi);
-  o.d = yv - te * q;                                                          // :162
+  double q;                                                                   // (y + phi) / (exp(theta) + phi)
+  if (ref_order) {
+    // per-row outputs (d/dalpha_i, d/dphi_i) are differences of O(1) terms: keep the reference's own
+    // operation order so that components that nearly cancel round the same way (:159-162, :180-183)
+    const double te = exp(theta);
+    q = ypp / (te + phi);
+    o.d = yv - te * q;
+  } else {
+    o.d = yv - ypp * ((pos ? 1.0 : e) * inv1pe);                              // :162
+    q = ypp * inv_phi * ((pos ? e : 1.0) * inv1pe);
+  }
   double lp = 0.0;
   if (flags & STAN_CUDA_LP_MAIN) lp -= ypp * lse;                             // :145-147
   if (flags & STAN_CUDA_LP_LINEAR) lp += yv * theta;                          // :148-150
@@ -241,28 +258,53 @@ __device__ __forceinline__ RowTerms nb_row_epilogue(double eta, double alpha, do
   return o;
 }
 
-// ordered_logistic_glm_lpmf.hpp:104-171, one row of class c (1 .. ncuts + 1); `cuts` in shared
-// memory.  t0 = log-density of the row, d = d1 - d2 (location derivative), t2 = d1, t3 = d2
-// (the row's contributions to d/dcuts[c-2] and d/dcuts[c-1], :192-200).
+// ordered_logistic_glm_lpmf.hpp:104-171.  Everything that depends on the class alone is tabulated once
+// per CTA in shared memory (ordered_class_table): for class c (1 .. ncuts + 1), with cy1 = cuts[c-1]
+// (+inf for the last class) and cy2 = cuts[c-2] (-inf for the first),
+//   tab[0][c-1] = cy1, tab[1][c-1] = cy2,
+//   tab[2][c-1] = ecd = exp(cy2 - cy1)                         (:164; 0 at the two ends)
+//   tab[3][c-1] = 1 / (1 - ecd)                                (:165-171)
+//   tab[4][c-1] = log1m_exp(cy2 - cy1)                         (:141; the reference evaluates it at
+//                 (loc - cy1) - (loc - cy2), the same number up to rounding of the location; 0 at the ends)
+// which leaves two exponentials, two log1p and two divisions per row.
+constexpr int kOrdTabRows = 5;
 __device__ __forceinline__ double log1m_exp_dev(double a) {  // prim/scal/fun/log1m_exp.hpp:44-54
   if (a >= 0) return nan("");
   return a > -0.693147 ? log(-expm1(a)) : log1p(-exp(a));
 }
-__device__ __forceinline__ RowTerms ordered_row_epilogue(double loc, int c, int ncuts, const double* cuts) {
-  RowTerms o;
-  const int ncls = ncuts + 1;
+template <int NT>
+__device__ __forceinline__ void ordered_class_table(const GlmKernelParams& p, double* tab, int tid) {
+  const int ncls = p.ncuts + 1;
   const double inf = __longlong_as_double(0x7ff0000000000000LL);
-  const double cy1 = c != ncls ? cuts[c - 1] : inf;                                   // :104-115
-  const double cy2 = c != 1 ? cuts[c - 2] : -inf;
-  const double cut2 = loc - cy2, cut1 = loc - cy1;                                    // :124-125
-  const double m1 = (cut1 > 0.0 ? -cut1 : 0.0) - log1p(exp(-fabs(cut1)));            // :128-129
-  const double m2 = (cut2 <= 0.0 ? cut2 : 0.0) - log1p(exp(-fabs(cut2)));            // :130-131
-  o.t0 = c == 1 ? m1 : (c == ncls ? m2 : m2 + log1m_exp_dev(cut1 - cut2) + m1);       // :137-144
-  const double ecd = exp(cy2 - cy1);                                                  // :164
-  const double s2 = cut2 > 0 ? exp(-cut2) / (1 + exp(-cut2)) : 1 / (1 + exp(cut2));   // :165-167
-  const double s1 = cut1 > 0 ? exp(-cut1) / (1 + exp(-cut1)) : 1 / (1 + exp(cut1));   // :168-171
-  const double d1 = s2 - ecd / (ecd - 1);
-  const double d2 = 1 / (1 - ecd) - s1;
+  for (int c = 1 + tid; c <= ncls; c += NT) {
+    const bool first = c == 1, last = c == ncls;
+    const double cy1 = last ? inf : kernel_param(p, p.kpad + 2 + c - 1);
+    const double cy2 = first ? -inf : kernel_param(p, p.kpad + 2 + c - 2);
+    const bool inner = !first && !last;
+    const double ecd = inner ? exp(cy2 - cy1) : 0.0;
+    tab[0 * ncls + c - 1] = cy1;
+    tab[1 * ncls + c - 1] = cy2;
+    tab[2 * ncls + c - 1] = ecd;
+    tab[3 * ncls + c - 1] = 1.0 / (1.0 - ecd);
+    tab[4 * ncls + c - 1] = inner ? log1m_exp_dev(cy2 - cy1) : 0.0;
+  }
+}
+// one row of class c: t0 = log-density of the row, d = d1 - d2 (location derivative), t2 = d1, t3 = d2
+// (the row's contributions to d/dcuts[c-2] and d/dcuts[c-1], :192-200)
+__device__ __forceinline__ RowTerms ordered_row_epilogue(double loc, int c, int ncls, const double* tab) {
+  RowTerms o;
+  const double cut1 = loc - tab[0 * ncls + c - 1], cut2 = loc - tab[1 * ncls + c - 1];  // :124-125
+  // exp(-|cut|) serves both the log-density (:128-131) and the derivative: for cut > 0 the reference
+  // uses exp(-cut) / (1 + exp(-cut)), else 1 / (1 + exp(cut)) (:165-171) -- the same exponential
+  const double e1 = exp(-fabs(cut1)), e2 = exp(-fabs(cut2));
+  const double m1 = (cut1 > 0.0 ? -cut1 : 0.0) - log1p(e1);                          // :128-129
+  const double m2 = (cut2 <= 0.0 ? cut2 : 0.0) - log1p(e2);                          // :130-131
+  o.t0 = c == 1 ? m1 : (c == ncls ? m2 : m2 + tab[4 * ncls + c - 1] + m1);            // :137-144
+  const double ecd = tab[2 * ncls + c - 1], r = tab[3 * ncls + c - 1];
+  const double s2 = (cut2 > 0 ? e2 : 1.0) / (1 + e2);                                 // :165-167
+  const double s1 = (cut1 > 0 ? e1 : 1.0) / (1 + e1);                                 // :168-171
+  const double d1 = s2 + ecd * r;  // s2 - ecd / (ecd - 1)
+  const double d2 = r - s1;        // 1 / (1 - ecd) - s1
   o.d = d1 - d2;                                                                      // :173
   o.t2 = d1;
   o.t3 = d2;

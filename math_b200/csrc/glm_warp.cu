@@ -47,8 +47,11 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   const int cols = kpad + 4 + ncuts;  // width of a partial: [lp, sum d, a2, a3, dbeta(kpad), dcuts(ncuts)]
   double* red = reinterpret_cast<double*>(smem + size_t(p.stages) * p.stage_bytes);  // [WARPS][cols]
   double* part = red + size_t(kWarpConsumers) * cols;                                // [8]
-  double* cuts_s = part + 8;                                                         // [ncuts]
-  uint64_t* full = reinterpret_cast<uint64_t*>(cuts_s + ncuts);                      // [stages]
+  double* ord_tab = part + 8;                                                        // [kOrdTabRows][ncuts + 1]
+  const int ord_doubles = FAMILY == STAN_CUDA_ORDERED_LOGISTIC ? kOrdTabRows * (ncuts + 1) : 0;
+  const bool ord_private = FAMILY == STAN_CUDA_ORDERED_LOGISTIC && p.ord_private;
+  double* ord_bins = ord_tab + ord_doubles;                                          // [ncuts][R] when ord_private
+  uint64_t* full = reinterpret_cast<uint64_t*>(ord_bins + (ord_private ? ncuts * R : 0));  // [stages]
   int* arrived = reinterpret_cast<int*>(full + p.stages);                            // [stages]
   __shared__ int s_flag;
 
@@ -74,9 +77,11 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
     mbar_fence_init();
   }
   if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
-    // cut-points into shared memory; the per-warp bins of d/dcuts (tail of each warp's row of `red`) start at zero
-    for (int j = tid; j < ncuts; j += NT) cuts_s[j] = kernel_param(p, kpad + 2 + j);
+    // per-class table into shared memory; the per-warp bins of d/dcuts (tail of each warp's row of `red`) start at zero
+    ordered_class_table<NT>(p, ord_tab, tid);
     for (int j = tid; j < kWarpConsumers * ncuts; j += NT) red[size_t(j / ncuts) * cols + kpad + 4 + j % ncuts] = 0.0;
+    if (ord_private)
+      for (int j = tid; j < ncuts * R; j += NT) ord_bins[j] = 0.0;
   }
   __syncthreads();
 
@@ -109,8 +114,9 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   }
   const double alpha0 = kernel_param(p, kpad);
   const double sigma0 = kernel_param(p, kpad + 1);
-  const double inv_sigma0 = FAMILY == STAN_CUDA_NORMAL_ID ? 1.0 / sigma0 : 1.0;
+  double inv_sigma0 = FAMILY == STAN_CUDA_NORMAL_ID ? 1.0 / sigma0 : 1.0;
   const double log_sigma0 = FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG ? log(sigma0) : 0.0;  // log phi
+  if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) inv_sigma0 = 1.0 / sigma0;
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // lp main, sum d, sum s^2, sum log sigma (cg == 0 lanes)
   const int r_in_tile = warp * rpw + rl;
 
@@ -163,22 +169,29 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
       if (p.alpha_vec) alpha = p.alpha_vec[row];
       if (FAMILY >= STAN_CUDA_NORMAL_ID && p.sigma_vec) {
         sigma_row = p.sigma_vec[row];
-        if (FAMILY == STAN_CUDA_NORMAL_ID) inv_sigma = 1.0 / sigma_row;
-        else log_sigma_row = log(sigma_row);
+        inv_sigma = 1.0 / sigma_row;
+        if (FAMILY != STAN_CUDA_NORMAL_ID) log_sigma_row = log(sigma_row);
       }
     }
     RowTerms o;
     if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
       const int c = valid ? int(yv) : 1;  // 1 <= c <= ncuts + 1 was checked from the range of y cached at fill
-      o = ordered_row_epilogue(eta, c, ncuts, cuts_s);
+      o = ordered_row_epilogue(eta, c, ncuts + 1, ord_tab);
       if (valid && cg == 0) {
         a0 += o.t0;
         a1 += o.d;
         a2 += eta;  // ordered_logistic_glm_lpmf.hpp:119: finiteness of sum(location)
       }
-      if ((p.flags & STAN_CUDA_NEED_DCUTS) && ncuts > 0) {
-        // d/dcuts (:192-200): one owner lane per row adds into this warp's bins, rows in order, so the
-        // sum is the same on every run (no floating-point atomics)
+      if ((p.flags & STAN_CUDA_NEED_DCUTS) && ord_private) {
+        // d/dcuts (:192-200), few classes: every row slot of the tile owns a private row of bins
+        // ([class][row slot]: conflict-free, no ordering question), summed in slot order at the end
+        if (valid && cg == 0) {
+          if (c != ncuts + 1) ord_bins[(c - 1) * R + r_in_tile] += o.t3;
+          if (c != 1) ord_bins[(c - 2) * R + r_in_tile] -= o.t2;
+        }
+      } else if ((p.flags & STAN_CUDA_NEED_DCUTS) && ncuts > 0) {
+        // many classes: one owner lane per row adds into this warp's bins, rows in order, so the sum is
+        // the same on every run (no floating-point atomics)
         double* bins = red + size_t(warp) * cols + kpad + 4;
         for (int r = 0; r < rpw; ++r) {
           if (rl == r && cg == 0 && valid) {
@@ -189,7 +202,7 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
         }
       }
     } else if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
-      o = nb_row_epilogue(eta, alpha, yv, sigma_row, log_sigma_row, p.flags, p.nb_rowfun != 0);
+      o = nb_row_epilogue(eta, alpha, yv, sigma_row, log_sigma_row, inv_sigma, p.flags, ROWIO && p.nb_rowfun != 0, ROWIO);
     } else {
       o = row_epilogue<FAMILY>(eta, alpha, yv, inv_sigma);
     }
@@ -247,8 +260,13 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
   for (int c = tid; c < cols; c += NT) {
     double sum = 0.0;
+    if (ord_private && c >= kpad + 4) {
+      const double* b = ord_bins + (c - kpad - 4) * R;
+      for (int r = 0; r < R; ++r) sum += b[r];
+    } else {
 #pragma unroll
-    for (int w = 0; w < kWarpConsumers; ++w) sum += red[size_t(w) * cols + c];
+      for (int w = 0; w < kWarpConsumers; ++w) sum += red[size_t(w) * cols + c];
+    }
     my_scratch[c] = sum;
   }
   double* fin = reinterpret_cast<double*>(stage0);  // [cols]; every stage has been consumed by now
@@ -260,10 +278,12 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
 // =============================================================================================
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+static bool ord_private_bins(const Tiling& t, int ncuts) { return ncuts > 0 && size_t(ncuts) * t.R <= size_t(kOrdPrivateDoubles); }
+
 static size_t warp_smem_bytes(const Tiling& t, int stages, int ncuts, size_t* stage_bytes_out) {
   const size_t stage = align_up(t.tile_bytes() + size_t(t.R) * sizeof(double), 128);
   if (stage_bytes_out) *stage_bytes_out = stage;
-  const size_t fixed = (size_t(kWarpConsumers) * (t.kpad + 4 + ncuts) + 8 + ncuts) * sizeof(double) + size_t(stages) * (sizeof(uint64_t) + sizeof(int)) + 8;
+  const size_t fixed = (size_t(kWarpConsumers) * (t.kpad + 4 + ncuts) + 8 + size_t(kOrdTabRows) * (ncuts + 1) + (ord_private_bins(t, ncuts) ? size_t(ncuts) * t.R : 0)) * sizeof(double) + size_t(stages) * (sizeof(uint64_t) + sizeof(int)) + 8;
   return size_t(stages) * stage + fixed;
 }
 
@@ -368,6 +388,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   p.group_size = group_size;
   p.stage_bytes = uint32_t(stage_bytes);
   p.blocked = tuning().blocked;
+  p.ord_private = ord_private_bins(t, ncuts) ? 1 : 0;
   const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
   switch (d->family) {
     case STAN_CUDA_BERNOULLI_LOGIT:
@@ -381,7 +402,8 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
                    : launch_warp_inst<STAN_CUDA_NORMAL_ID, false>(p, grid, smem, stream);
     case STAN_CUDA_NEG_BINOMIAL_2_LOG:
       SC_TRY(prepare_neg_binomial(d, io, ws, &p, stream));
-      return rowio ? launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, true>(p, grid, smem, stream)
+      // per-row lgamma / digamma (vector phi, or outcomes beyond the histogram) live in the ROWIO instantiation only
+      return (rowio || p.nb_rowfun) ? launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, true>(p, grid, smem, stream)
                    : launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, false>(p, grid, smem, stream);
     case STAN_CUDA_ORDERED_LOGISTIC:
       if (rowio) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic has no per-row operands");

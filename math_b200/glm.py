@@ -383,6 +383,10 @@ class GlmData:
         check(lib().stan_cuda_glm_launch(self.h, flags, d_params, d_alpha_vec, d_sigma_vec, d_result,
                                          d_row_dalpha, d_row_dsigma, stream))
 
+    def launch_ordered(self, flags, d_params, ncuts, d_result, stream):
+        """ordered_logistic: d_params = [beta(kpad), 0, 0, cuts], d_result = [4 + kpad + ncuts]."""
+        check(lib().stan_cuda_glm_launch_ordered(self.h, flags, d_params, ncuts, d_result, stream))
+
     def close(self):
         if self.h:
             lib().stan_cuda_data_destroy(self.h)

@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--stages", type=int, default=0)
     ap.add_argument("--ctas", type=int, default=0)
     ap.add_argument("--shapes", default="")
+    ap.add_argument("--widened", action="store_true", help="neg_binomial_2_log and ordered_logistic shapes instead")
     args = ap.parse_args()
     import torch
     from bench import FAM_ID, measured_peak, synth_shard
@@ -34,6 +35,8 @@ def main():
     if args.shapes:
         shapes = [(f, int(n), int(k)) for f, n, k in (sh.split(":") for sh in args.shapes.split(","))]
     stream = torch.cuda.Stream()
+    if args.widened:
+        return widened(args, torch, glm, peak, stream)
     for family, n, k in shapes:
         x, y, alpha, beta, sigma = synth_shard(family, n, k, seed=1)
         fam = FAM_ID[family]
@@ -60,6 +63,54 @@ def main():
             print(json.dumps({"kernel": kern, "family": family, "n": n, "k": k, "us": round(ms * 1e3, 2),
                               "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "lp": float(dr[0])}), flush=True)
             data.close()
+        del x, y
+
+
+def widened(args, torch, glm, peak, stream):
+    """SURVEY 8(f) rank 1 families on the warp kernel: neg_binomial_2_log (scalar phi: histogram path) and
+    ordered_logistic (C classes), same timing method."""
+    from bench import synth_shard
+    from math_b200 import _abi
+    cases = [("neg_binomial_2_log", 1_250_000, 128, 0), ("neg_binomial_2_log", 1_000_000, 32, 0),
+             ("ordered_logistic", 1_250_000, 128, 5), ("ordered_logistic", 1_000_000, 32, 5),
+             ("ordered_logistic", 1_000_000, 32, 64)]
+    for family, n, k, ncls in cases:
+        x, y, alpha, beta, _ = synth_shard("poisson_log", n, k, seed=1)
+        fam = _abi.FAMILIES[family]
+        ncuts = 0
+        if fam == _abi.ORDERED_LOGISTIC:
+            y = (1 + (y + np.arange(n)) % ncls).astype(np.int32)
+            ncuts = ncls - 1
+            flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+        else:
+            flags = glm.glm_flags(fam, False)
+        data = glm.GlmData(fam, x, y)
+        params = np.zeros(data.params_len + ncuts)
+        params[:k], params[data.kpad], params[data.kpad + 1] = beta, alpha[0], 2.5
+        params[data.kpad + 2:] = np.linspace(-1.5, 1.5, ncuts)
+        dp = torch.from_numpy(params).cuda()
+        dr = torch.zeros(data.result_len + ncuts, dtype=torch.float64, device="cuda")
+
+        def go():
+            if ncuts:
+                data.launch_ordered(flags, dp.data_ptr(), ncuts, dr.data_ptr(), stream.cuda_stream)
+            else:
+                data.launch(flags, dp.data_ptr(), dr.data_ptr(), stream.cuda_stream)
+        with torch.cuda.stream(stream):
+            for _ in range(5):
+                go()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(args.reps):
+                go()
+            e1.record(stream)
+        stream.synchronize()
+        ms = e0.elapsed_time(e1) / args.reps
+        gbs = data.algorithmic_bytes / (ms * 1e-3) / 1e9
+        print(json.dumps({"kernel": "warp", "family": family, "n": n, "k": k, "classes": ncls, "us": round(ms * 1e3, 2),
+                          "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "lp": float(dr[0]),
+                          "launches_per_eval": 2 if (fam == _abi.NEG_BINOMIAL_2_LOG) else 1}), flush=True)
+        data.close()
         del x, y
 
 

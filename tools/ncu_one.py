@@ -1,19 +1,39 @@
-import sys, os
+"""One shape, three launches of the GLM kernel: the target of `ncu --set full -k regex:glm_warp_kernel -s 2 -c 1`.
+usage: ncu_one.py FAMILY N K warp|cta [CLASSES]"""
+import os
+import sys
+
 sys.path.insert(0, os.getcwd())
-import numpy as np, torch
-from bench import FAM_ID, synth_shard
-from math_b200 import glm
+import numpy as np
+import torch
+
+from bench import synth_shard
+from math_b200 import _abi, glm
 from math_b200._lib import lib
+
 family, n, k, kern = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), sys.argv[4]
+ncls = int(sys.argv[5]) if len(sys.argv) > 5 else 5
 glm.init(1)
 lib().stan_cuda_set_kernel(1 if kern == "warp" else 0)
-x, y, alpha, beta, sigma = synth_shard(family, n, k, seed=1)
-fam = FAM_ID[family]
+fam = _abi.FAMILIES[family]
+x, y, alpha, beta, sigma = synth_shard(family if fam <= _abi.NORMAL_ID else "poisson_log", n, k, seed=1)
+ncuts = 0
+flags = glm.glm_flags(fam, False) if fam != _abi.ORDERED_LOGISTIC else (_abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS)
+if fam == _abi.ORDERED_LOGISTIC:
+    y = (1 + (y + np.arange(n)) % ncls).astype(np.int32)
+    ncuts = ncls - 1
 data = glm.GlmData(fam, x, y)
-params = np.zeros(data.params_len); params[:k] = beta; params[data.kpad] = alpha[0]; params[data.kpad+1] = 1.0
-dp = torch.from_numpy(params).cuda(); dr = torch.zeros(data.result_len, dtype=torch.float64, device="cuda")
+params = np.zeros(data.params_len + ncuts)
+params[:k], params[data.kpad] = beta, alpha[0]
+params[data.kpad + 1] = 2.5 if fam == _abi.NEG_BINOMIAL_2_LOG else 1.0
+params[data.kpad + 2:] = np.linspace(-1.5, 1.5, ncuts)
+dp = torch.from_numpy(params).cuda()
+dr = torch.zeros(data.result_len + ncuts, dtype=torch.float64, device="cuda")
 s = torch.cuda.Stream()
 for _ in range(3):
-    data.launch(glm.glm_flags(fam, False), dp.data_ptr(), dr.data_ptr(), s.cuda_stream)
+    if ncuts:
+        data.launch_ordered(flags, dp.data_ptr(), ncuts, dr.data_ptr(), s.cuda_stream)
+    else:
+        data.launch(flags, dp.data_ptr(), dr.data_ptr(), s.cuda_stream)
 s.synchronize()
 print(float(dr[0]))
