@@ -17,6 +17,7 @@
  *                                  stan/math/opencl/kernels/matrix_multiply.hpp:354-386 (row_vector_matrix_multiply)
  *                                  neg_binomial_2_log_glm_lpmf stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:108-197
  *                                  ordered_logistic_glm_lpmf   stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:93-199
+ *                                  categorical_logit_glm_lpmf  stan/math/prim/mat/prob/categorical_logit_glm_lpmf.hpp:74-190
  *   stan_cuda_normal_lpdf_eval   the loop of normal_lpdf      stan/math/prim/scal/prob/normal_lpdf.hpp:67-110
  *   stan_cuda_data_* / cache_*   matrix_cl + to_matrix_cl      stan/math/opencl/matrix_cl.hpp:32-454, stan/math/opencl/copy.hpp:37-93
  *                                and the cache-by-call_id of the MPI backend
@@ -35,7 +36,8 @@
  *    2  STAN_CUDA_BAD_OUTCOME the device-resident outcome vector violates the family's domain (bernoulli:
  *                             outside [0, 1], bernoulli_logit_glm_lpmf.hpp:70; poisson: negative,
  *                             poisson_log_glm_lpmf.hpp:70; ordered_logistic: outside [1, cuts_len + 1],
- *                             ordered_logistic_glm_lpmf.hpp:78).  The range of y is computed ONCE, on the device,
+ *                             ordered_logistic_glm_lpmf.hpp:78; categorical_logit: outside [1, n_classes],
+ *                             categorical_logit_glm_lpmf.hpp:63).  The range of y is computed ONCE, on the device,
  *                             when y is cached (the data is immutable), so the per-call O(N) host loop of
  *                             check_bounded / check_nonnegative disappears; nothing was evaluated; the C++
  *                             wrapper runs the reference's own check to throw the same std::domain_error
@@ -81,6 +83,7 @@ extern "C" {
 #define STAN_CUDA_NORMAL_ID 2
 #define STAN_CUDA_NEG_BINOMIAL_2_LOG 3 /* precision phi travels in the sigma slot, d/dphi in dsigma */
 #define STAN_CUDA_ORDERED_LOGISTIC 4   /* no intercept; cut-points in cuts[cuts_len], d/dcuts in dcuts; y in 1..cuts_len+1 */
+#define STAN_CUDA_CATEGORICAL_LOGIT 5  /* n_classes columns: beta is k x n_classes (column-major), alpha[n_classes]; y in 1..n_classes */
 
 /* flags: which summands of the log-density to include (the reference decides this at compile
  * time with include_summand<propto, ...>, stan/math/prim/scal/meta/include_summand.hpp) and
@@ -105,7 +108,7 @@ extern "C" {
 #define STAN_CUDA_FUSED_ALLREDUCE 0x100u
 
 typedef struct stan_cuda_glm_args {
-  int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID | NEG_BINOMIAL_2_LOG | ORDERED_LOGISTIC */
+  int32_t family;      /* STAN_CUDA_BERNOULLI_LOGIT | POISSON_LOG | NORMAL_ID | NEG_BINOMIAL_2_LOG | ORDERED_LOGISTIC | CATEGORICAL_LOGIT */
   uint32_t flags;      /* STAN_CUDA_LP_* | STAN_CUDA_NEED_* */
   int64_t n;           /* rows of x (instances) */
   int64_t k;           /* columns of x (attributes) */
@@ -130,6 +133,10 @@ typedef struct stan_cuda_glm_args {
   const double* cuts;  /* host; cuts_len ascending cut-points (number of classes - 1) */
   int64_t cuts_len;
   double* dcuts;       /* [cuts_len] */
+  /* categorical_logit only (stan/math/prim/mat/prob/categorical_logit_glm_lpmf.hpp:38-42): alpha has
+   * n_classes entries (alpha_len = n_classes), beta is k x n_classes column-major, dalpha[n_classes],
+   * dbeta[k * n_classes] */
+  int64_t n_classes;
 } stan_cuda_glm_args;
 
 typedef struct stan_cuda_normal_args {
@@ -245,6 +252,10 @@ STAN_CUDA_API int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const
  * dbeta(k_pad), dcuts(ncuts)]; the caller has checked 1 <= y <= ncuts + 1 (stan_cuda_data_y_range). */
 STAN_CUDA_API int stan_cuda_glm_launch_ordered(stan_cuda_data_t d, uint32_t flags, const double* d_params, int ncuts,
                                  double* d_result, void* stream);
+/* categorical_logit: d_params = [beta as n_classes rows of k_pad (class-major, zero padded), alpha(n_classes)],
+ * d_result = [lp, 0, 0, status, dalpha(n_classes), dbeta as n_classes rows of k_pad]. */
+STAN_CUDA_API int stan_cuda_glm_launch_categorical(stan_cuda_data_t d, uint32_t flags, const double* d_params,
+                                     int n_classes, double* d_result, void* stream);
 /* All-reduce (sum) `count` doubles in place across the ranks of the communicator, on `stream`. */
 STAN_CUDA_API int stan_cuda_allreduce(double* d_buf, int64_t count, void* stream);
 /* Number of this library's kernels launched per stan_cuda_glm_launch call for this data. */

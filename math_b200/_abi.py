@@ -10,8 +10,10 @@ OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND = 0, 1, 2, 3
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
 
 BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID, NEG_BINOMIAL_2_LOG, ORDERED_LOGISTIC = 0, 1, 2, 3, 4
+CATEGORICAL_LOGIT = 5
 FAMILIES = {"bernoulli_logit": BERNOULLI_LOGIT, "poisson_log": POISSON_LOG, "normal_id": NORMAL_ID,
-            "neg_binomial_2_log": NEG_BINOMIAL_2_LOG, "ordered_logistic": ORDERED_LOGISTIC}
+            "neg_binomial_2_log": NEG_BINOMIAL_2_LOG, "ordered_logistic": ORDERED_LOGISTIC,
+            "categorical_logit": CATEGORICAL_LOGIT}
 HAS_SCALE = (NORMAL_ID, NEG_BINOMIAL_2_LOG)   # families with a fifth operand (sigma | phi)
 
 LP_CONST, LP_SCALE, LP_MAIN, LP_ALL = 0x01, 0x02, 0x04, 0x07
@@ -48,6 +50,7 @@ class GlmArgs(C.Structure):
         ("cuts", C.c_void_p),
         ("cuts_len", C.c_int64),
         ("dcuts", C.c_void_p),
+        ("n_classes", C.c_int64),
     ]
 
 
@@ -118,6 +121,7 @@ PROTOTYPES = {
     "stan_cuda_glm_launch": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "stan_cuda_glm_launch_ordered": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "stan_cuda_glm_launch_categorical": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "stan_cuda_allreduce": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p]),
     "stan_cuda_data_launches_per_eval": (C.c_int, [C.c_void_p]),
     "stan_cuda_data_y_range": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

@@ -162,11 +162,16 @@ static inline bool has_scale(int family) {
 
 static int check_glm_args(const stan_cuda_glm_args* a) {
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null args");
-  if (a->family < 0 || a->family > STAN_CUDA_ORDERED_LOGISTIC) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: unknown family");
+  if (a->family < 0 || a->family > STAN_CUDA_CATEGORICAL_LOGIT) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: unknown family");
   if (a->n < 0 || a->k < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: negative size");
   if (a->n > 0 && (!a->y || (!a->x && a->k > 0))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null x or y");
   if (a->k > 0 && !a->beta) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null beta");
-  if (a->family == STAN_CUDA_ORDERED_LOGISTIC) {
+  if (a->family == STAN_CUDA_CATEGORICAL_LOGIT) {
+    if (a->n_classes < 1 || !a->alpha || a->alpha_len != a->n_classes)
+      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit needs n_classes >= 1 and alpha_len == n_classes");
+    if (a->n_classes > kMaxClasses)
+      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit supports at most 16 classes on the device");
+  } else if (a->family == STAN_CUDA_ORDERED_LOGISTIC) {
     if (a->cuts_len < 0 || (a->cuts_len > 0 && !a->cuts)) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null cuts");
     if (a->cuts_len > kMaxCuts)
       return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: ordered_logistic supports at most 256 cut-points on the device");
@@ -207,8 +212,14 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (a->lp) *a->lp = 0.0;
     if (a->dbeta) for (int64_t j = 0; j < a->k; ++j) a->dbeta[j] = 0.0;
     if (a->family == STAN_CUDA_ORDERED_LOGISTIC && a->dcuts) for (int64_t j = 0; j < a->cuts_len; ++j) a->dcuts[j] = 0.0;
+    if (a->family == STAN_CUDA_CATEGORICAL_LOGIT) {
+      if (a->dbeta) for (int64_t j = 0; j < a->k * a->n_classes; ++j) a->dbeta[j] = 0.0;
+      if (a->dalpha) for (int64_t j = 0; j < a->n_classes; ++j) a->dalpha[j] = 0.0;
+    }
     return STAN_CUDA_OK;
   }
+  const bool categorical = a->family == STAN_CUDA_CATEGORICAL_LOGIT;
+  const size_t ncls = categorical ? size_t(a->n_classes) : 0;
   const bool ordered = a->family == STAN_CUDA_ORDERED_LOGISTIC;
   const size_t ncuts = ordered ? size_t(a->cuts_len) : 0;
   SC_TRY(ensure_init());
@@ -225,11 +236,13 @@ int glm_eval(const stan_cuda_glm_args* a) {
     }
     if (ordered) {  // ordered_logistic_glm_lpmf.hpp:78 check_bounded(y, 1, N_classes)
       if (lo < 1 || hi > int64_t(ncuts) + 1) return STAN_CUDA_BAD_OUTCOME;
+    } else if (categorical) {  // categorical_logit_glm_lpmf.hpp:63-64
+      if (lo < 1 || hi > int64_t(ncls)) return STAN_CUDA_BAD_OUTCOME;
     } else if (lo < 0 || (a->family == STAN_CUDA_BERNOULLI_LOGIT && hi > 1)) {
       return STAN_CUDA_BAD_OUTCOME;
     }
   }
-  const bool alpha_vec = !ordered && a->alpha_len != 1;
+  const bool alpha_vec = !ordered && !categorical && a->alpha_len != 1;
   const bool sigma_vec = has_scale(a->family) && a->sigma_len != 1;
   const bool want_rowa = ((a->flags & STAN_CUDA_NEED_DALPHA) && alpha_vec && a->dalpha) ||
                          ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID);
@@ -256,13 +269,17 @@ int glm_eval(const stan_cuda_glm_args* a) {
 
   std::vector<ShardRun> runs(S);
   const int kpad = e->shards[0].d->t.kpad;
-  const size_t np = size_t(kpad) + 2 + ncuts, nr = size_t(kpad) + 4 + ncuts;
+  if (categorical && ncls * size_t(kpad) > size_t(kMaxClassWeights))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit supports classes * k_pad <= 4096 on the device");
+  const size_t np = categorical ? ncls * (size_t(kpad) + 1) : size_t(kpad) + 2 + ncuts;
+  const size_t nr = categorical ? 4 + ncls * (size_t(kpad) + 1) : size_t(kpad) + 4 + ncuts;
+  if (xchg && nr > size_t(kXchgCols)) xchg = nullptr;  // result block wider than an exchange slot: NCCL behind the kernel
   // Low-latency path (no per-row vectors in or out, and no separate collective behind the kernel):
   // the parameter block travels in the kernel arguments, the kernel writes the result block and a
   // completion flag straight into mapped pinned host memory, the host spins on the flag.  Saves the
   // H2D copy, the D2H copy and the stream synchronisation of the general path (~15 us per call).
   const bool per_row = alpha_vec || sigma_vec || want_rowa || want_rows;
-  const bool low_latency = !per_row && low_latency_enabled() && ((S == 1 && world == 1) || xchg != nullptr) &&
+  const bool low_latency = !per_row && !categorical && low_latency_enabled() && ((S == 1 && world == 1) || xchg != nullptr) &&
                            np <= size_t(kInlineParams);
   for (size_t s = 0; s < S; ++s) {
     stan_cuda_data* d = e->shards[s].d;
@@ -287,10 +304,17 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (want_rowa) { run.d_rowa = p; p += rows_al; }
     if (want_rows) { run.d_rows = p; p += rows_al; }
     double* hp = td->h_pinned;
-    for (int j = 0; j < kpad; ++j) hp[j] = j < a->k ? a->beta[j] : 0.0;
-    hp[kpad] = (alpha_vec || ordered) ? 0.0 : a->alpha[0];
-    for (size_t j = 0; j < ncuts; ++j) hp[kpad + 2 + j] = a->cuts[j];
-    hp[kpad + 1] = (has_scale(a->family) && !sigma_vec) ? a->sigma[0] : 1.0;
+    if (categorical) {  // weights class-major, every class padded to kpad; intercepts behind
+      for (size_t c = 0; c < ncls; ++c) {
+        for (int j = 0; j < kpad; ++j) hp[c * kpad + j] = j < a->k ? a->beta[c * a->k + j] : 0.0;
+        hp[ncls * kpad + c] = a->alpha[c];
+      }
+    } else {
+      for (int j = 0; j < kpad; ++j) hp[j] = j < a->k ? a->beta[j] : 0.0;
+      hp[kpad] = (alpha_vec || ordered) ? 0.0 : a->alpha[0];
+      hp[kpad + 1] = (has_scale(a->family) && !sigma_vec) ? a->sigma[0] : 1.0;
+      for (size_t j = 0; j < ncuts; ++j) hp[kpad + 2 + j] = a->cuts[j];
+    }
     if (!low_latency)
       SC_CUDA(cudaMemcpyAsync(run.d_params, hp, np * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     if (alpha_vec)
@@ -299,6 +323,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
       SC_CUDA(cudaMemcpyAsync(run.d_sigma, a->sigma + r0, size_t(rows) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     LaunchIO io{a->flags, run.d_params, run.d_alpha, run.d_sigma, run.d_result, run.d_rowa, run.d_rows};
     io.ncuts = int(ncuts);
+    io.ncls = int(ncls);
     if (xchg) {
       io.xchg = S > 1 ? &xchg[s] : xchg;
       io.xchg_seq = xchg_seq;
@@ -370,8 +395,12 @@ int glm_eval(const stan_cuda_glm_args* a) {
   }
   const double* res = runs[0].td->h_pinned + np;
   if (a->lp) *a->lp = res[0];
-  if ((a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) memcpy(a->dbeta, res + 4, size_t(a->k) * sizeof(double));
-  if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha && !alpha_vec && !ordered) a->dalpha[0] = res[1];
+  if (categorical) {
+    if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha) memcpy(a->dalpha, res + 4, ncls * sizeof(double));
+    if ((a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta)
+      for (size_t c = 0; c < ncls; ++c) memcpy(a->dbeta + c * a->k, res + 4 + ncls + c * kpad, size_t(a->k) * sizeof(double));
+  } else if ((a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) memcpy(a->dbeta, res + 4, size_t(a->k) * sizeof(double));
+  if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha && !alpha_vec && !ordered && !categorical) a->dalpha[0] = res[1];
   if (ordered && (a->flags & STAN_CUDA_NEED_DCUTS) && a->dcuts) memcpy(a->dcuts, res + 4 + kpad, ncuts * sizeof(double));
   if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma && has_scale(a->family) && !sigma_vec)
     a->dsigma[0] = res[2];

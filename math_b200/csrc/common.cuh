@@ -111,7 +111,12 @@ struct LaunchIO {
   // ordered_logistic: cut-points follow the parameter block (d_params[kpad + 2 + j]), d/dcuts follow
   // the result block (d_result[kpad + 4 + j])
   int ncuts = 0;
+  // categorical_logit: d_params = [beta: ncls rows of kpad (class-major), alpha(ncls)],
+  // d_result = [lp, 0, 0, status, dalpha(ncls), dbeta: ncls rows of kpad]
+  int ncls = 0;
 };
+constexpr int kMaxClasses = 16;              // categorical_logit: classes on the device path
+constexpr int kMaxClassWeights = 4096;       // categorical_logit: classes * k_pad (weights live in shared memory)
 constexpr int kMaxCuts = 256;                // ordered_logistic: per-warp bins live in shared memory
 constexpr int kOrdPrivateDoubles = 2048;     // ordered_logistic: ncuts * R up to this -> one private bin row per row slot
 constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sigma)
@@ -119,6 +124,12 @@ constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sig
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+// width of the result block (and of every partial) of one launch
+inline size_t result_cols(const stan_cuda_data* d, const LaunchIO& io) {
+  if (d->family == STAN_CUDA_CATEGORICAL_LOGIT) return size_t(4) + size_t(io.ncls) * (d->t.kpad + 1);
+  return size_t(d->t.kpad) + 4 + (d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0);
+}
 int sm_count(int device);
 
 // tuning knobs (env STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM; 0 = auto)

@@ -247,7 +247,7 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
                     int x_row_major, const void* y, int y_is_double, int64_t row0, cudaStream_t stream,
                     stan_cuda_data** out) {
   if (n_rows <= 0 || k < 0 || (!x && k > 0) || !y) return fail(STAN_CUDA_ERR_ARG, "data block: bad shape or null pointer");
-  if (family < 0 || family > STAN_CUDA_ORDERED_LOGISTIC) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
+  if (family < 0 || family > STAN_CUDA_CATEGORICAL_LOGIT) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
   stan_cuda_data* d = new stan_cuda_data();
   d->device = device;
   d->family = family;
@@ -341,9 +341,20 @@ int stan_cuda_glm_launch(stan_cuda_data_t d, uint32_t flags, const double* d_par
                          const double* d_sigma_vec, double* d_result, double* d_row_dalpha,
                          double* d_row_dsigma, void* stream) {
   if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: null argument");
-  if (d->family == STAN_CUDA_ORDERED_LOGISTIC)
-    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: ordered_logistic data goes through stan_cuda_glm_launch_ordered");
+  if (d->family == STAN_CUDA_ORDERED_LOGISTIC || d->family == STAN_CUDA_CATEGORICAL_LOGIT)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch: ordered_logistic / categorical_logit data goes through "
+                                   "stan_cuda_glm_launch_ordered / _categorical");
   LaunchIO io{flags, d_params, d_alpha_vec, d_sigma_vec, d_result, d_row_dalpha, d_row_dsigma};
+  return glm_launch_common(d, flags, io, stream);
+}
+
+int stan_cuda_glm_launch_categorical(stan_cuda_data_t d, uint32_t flags, const double* d_params, int n_classes,
+                                     double* d_result, void* stream) {
+  if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_categorical: null argument");
+  if (d->family != STAN_CUDA_CATEGORICAL_LOGIT)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_categorical: data block of another family");
+  LaunchIO io{flags, d_params, nullptr, nullptr, d_result, nullptr, nullptr};
+  io.ncls = n_classes;
   return glm_launch_common(d, flags, io, stream);
 }
 

@@ -34,6 +34,7 @@ struct GlmKernelParams {
   const double* nb_sums;  // neg_binomial_2_log with a histogram of y: [sum lgamma(y+phi), sum digamma(y+phi)]
   int nb_rowfun;          // neg_binomial_2_log: per-row lgamma/digamma (vector phi or no histogram)
   int ncuts;              // ordered_logistic: number of cut-points (classes - 1); 0 otherwise
+  int ncls, cat_groups;   // categorical_logit: classes; class groups of the gradient phase (glm_categorical.cu)
   int ord_private;        // ordered_logistic: d/dcuts bins private to each row slot of the tile ([ncuts][R] in shared memory)
   // low-latency host path: parameters by value, completion flag in mapped host memory
   int inline_n;                        // > 0: read the parameter block from inline_params
@@ -417,6 +418,9 @@ __device__ __forceinline__ void finish_reduction(const GlmKernelParams& p, int t
       if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;  // :102-108
       if (p.flags & STAN_CUDA_LP_MAIN) lp += A0;             // :109-112
       witness = A1;  // poisson_log_glm_lpmf.hpp:97 tests sum(theta_derivative)
+    } else if (FAMILY == STAN_CUDA_CATEGORICAL_LOGIT) {
+      if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
+      witness = A0;  // categorical_logit_glm_lpmf.hpp:109 tests logp
     } else if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
       if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
       witness = A2;  // ordered_logistic_glm_lpmf.hpp:119 tests sum(location)

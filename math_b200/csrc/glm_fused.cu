@@ -346,6 +346,8 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->nb_rowfun = 1;
   p->ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
   p->ord_private = 0;
+  p->ncls = 0;
+  p->cat_groups = 1;
   if (p->ncuts < 0 || p->ncuts > kMaxCuts) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
   p->x = d->x;
   p->y = d->y;
@@ -370,7 +372,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->host_flag = io.host_flag;
   p->host_seq = io.host_seq;
   const int np = t.kpad + 2 + p->ncuts;
-  if (io.h_params_inline && np <= kInlineParams) {
+  if (io.h_params_inline && np <= kInlineParams && d->family != STAN_CUDA_CATEGORICAL_LOGIT) {
     p->inline_n = np;
     for (int i = 0; i < np; ++i) p->inline_params[i] = io.h_params_inline[i];
   } else if (!io.d_params) {
@@ -382,7 +384,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->xchg_local = nullptr;
   for (int q = 0; q < kXchgMaxWorld; ++q) p->xchg_peers[q] = nullptr;
   if (io.xchg && io.xchg->world > 1) {
-    if (t.kpad + 4 + p->ncuts > kXchgCols) return fail(STAN_CUDA_ERR_ARG, "launch_glm: result block exceeds the exchange slot");
+    if (result_cols(d, io) > size_t(kXchgCols)) return fail(STAN_CUDA_ERR_ARG, "launch_glm: result block exceeds the exchange slot");
     p->xchg_world = io.xchg->world;
     p->xchg_rank = io.xchg->rank;
     p->xchg_local = io.xchg->local;
@@ -396,6 +398,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
 
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
+  if (d->family == STAN_CUDA_CATEGORICAL_LOGIT) return launch_glm_categorical(d, io, ws, stream);
   if (t.layout == kLayoutWarp) return launch_glm_warp(d, io, ws, stream);
   if (d->family >= STAN_CUDA_NEG_BINOMIAL_2_LOG)
     return fail(STAN_CUDA_ERR_ARG, "launch_glm: neg_binomial_2_log and ordered_logistic run on the warp kernel only");

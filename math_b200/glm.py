@@ -322,6 +322,70 @@ def ordered_logistic_glm_lpmf(y, x, beta, cuts, propto=False, beta_var=True, cut
     return r["lp"], grads
 
 
+def categorical_logit_glm_eval(y, x, alpha, beta, flags):
+    """Raw C-ABI call for family CATEGORICAL_LOGIT; beta is (k, C).  dict with rc, lp, dalpha (C), dbeta (k, C)."""
+    x, row_major, ldx = _prep_x(x)
+    n, k = x.shape
+    y = np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+    alpha = _f64(alpha)
+    beta = np.asfortranarray(np.asarray(beta, dtype=np.float64).reshape(k, -1))
+    ncls = beta.shape[1]
+    a = _abi.GlmArgs()
+    lp, dalpha, aux = np.zeros(1), np.zeros(max(ncls, 1)), np.zeros(4)
+    dbeta = np.zeros((max(k, 1), max(ncls, 1)), order="F")
+    a.family, a.flags, a.n, a.k, a.n_classes = _abi.CATEGORICAL_LOGIT, flags, n, k, ncls
+    a.x, a.ldx, a.x_row_major = x.ctypes.data, ldx, row_major
+    a.y, a.y_is_double = y.ctypes.data, 0
+    a.alpha, a.alpha_len, a.beta = alpha.ctypes.data, alpha.size, beta.ctypes.data
+    a.lp, a.dbeta, a.dalpha, a.aux = lp.ctypes.data, dbeta.ctypes.data, dalpha.ctypes.data, aux.ctypes.data
+    rc = check(lib().stan_cuda_glm_eval(C.byref(a)))
+    return {"rc": rc, "lp": float(lp[0]), "dalpha": dalpha[:ncls].copy(),
+            "dbeta": dbeta.reshape(-1, order="F")[:k * ncls].reshape((k, ncls), order="F").copy(), "_keep": (x, y)}
+
+
+def categorical_logit_glm_lpmf(y, x, alpha, beta, propto=False, alpha_var=True, beta_var=True):
+    """stan/math/prim/mat/prob/categorical_logit_glm_lpmf.hpp:38-42; beta is (k, C); grads: alpha, beta.
+    Checks in the reference's order (:56-64); the outcome range comes from the device."""
+    function = "categorical_logit_glm_lpmf"
+    xa = np.asarray(x, dtype=np.float64)
+    be = np.asarray(beta, dtype=np.float64)
+    if xa.ndim != 2 or be.ndim != 2:
+        raise ValueError("%s: x and beta must be matrices" % function)
+    n, k = xa.shape
+    ncls = be.shape[1]
+    ya = np.atleast_1d(np.asarray(y))
+    al = _f64(alpha) if np.size(alpha) else np.zeros(0)
+    if ya.size != n:
+        raise ValueError("%s: Vector of dependent variables has dimension = %d, expecting dimension = %d"
+                         % (function, ya.size, n))
+    if al.size != ncls:
+        raise ValueError("%s: Intercept vector has dimension = %d, expecting dimension = %d" % (function, al.size, ncls))
+    if be.shape[0] != k:
+        raise ValueError("%s: x.cols() (%d) and beta.rows() (%d) must match in size" % (function, k, be.shape[0]))
+    y_error = DomainError("%s: categorical outcome out of support must be in the interval [1, %d]" % (function, ncls))
+    if n == 0 or ncls == 1 or (propto and not (alpha_var or beta_var)):
+        if n and (ya.min() < 1 or ya.max() > ncls):     # nothing goes to the device: the outcome check runs here
+            raise y_error
+        return 0.0, {}
+    flags = _abi.LP_MAIN | (_abi.NEED_DBETA if beta_var else 0) | (_abi.NEED_DALPHA if alpha_var else 0)
+    r = categorical_logit_glm_eval(ya, xa, al, be, flags)
+    if r["rc"] == _abi.BAD_OUTCOME:
+        raise y_error
+    if r["rc"] == _abi.NONFINITE:       # :109-113
+        if not np.all(np.isfinite(be)):
+            raise DomainError("%s: Weight vector is not finite" % function)
+        if not np.all(np.isfinite(al)):
+            raise DomainError("%s: Intercept is not finite" % function)
+        if not np.all(np.isfinite(xa)):
+            raise DomainError("%s: Matrix of independent variables is not finite" % function)
+    grads = {}
+    if alpha_var:
+        grads["alpha"] = r["dalpha"]
+    if beta_var:
+        grads["beta"] = r["dbeta"]
+    return r["lp"], grads
+
+
 def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
     """normal_lpdf(y | mu, sigma) with mu and sigma as the differentiated operands."""
     function = "normal_lpdf"
@@ -386,6 +450,10 @@ class GlmData:
     def launch_ordered(self, flags, d_params, ncuts, d_result, stream):
         """ordered_logistic: d_params = [beta(kpad), 0, 0, cuts], d_result = [4 + kpad + ncuts]."""
         check(lib().stan_cuda_glm_launch_ordered(self.h, flags, d_params, ncuts, d_result, stream))
+
+    def launch_categorical(self, flags, d_params, n_classes, d_result, stream):
+        """categorical_logit: d_params = [beta: C rows of kpad, alpha(C)], d_result = [4 + C + C * kpad]."""
+        check(lib().stan_cuda_glm_launch_categorical(self.h, flags, d_params, n_classes, d_result, stream))
 
     def close(self):
         if self.h:

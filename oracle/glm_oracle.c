@@ -254,8 +254,50 @@ static int ordered_logistic_glm(const stan_cuda_glm_args* a, double* d) {
   return isfinite(witness) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+/* categorical_logit_glm_lpmf.hpp:74-190: lin = x * beta + alpha' (n x C), row-wise softmax.
+ * beta is k x C column-major, dbeta likewise; writes lp, dalpha[C], dbeta[k*C] itself. */
+static int categorical_logit_glm(const stan_cuda_glm_args* a) {
+  const int64_t n = a->n, k = a->k, C = a->n_classes;
+  double* lin = (double*)calloc((size_t)(C > 0 ? C : 1), sizeof(double));
+  double* e = (double*)calloc((size_t)(C > 0 ? C : 1), sizeof(double));
+  if (!lin || !e) { free(lin); free(e); return STAN_CUDA_ERR_ARG; }
+  const int want_da = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha;
+  const int want_db = (a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta;
+  if (want_da) for (int64_t c = 0; c < C; ++c) a->dalpha[c] = 0.0;
+  if (want_db) for (int64_t q = 0; q < k * C; ++q) a->dbeta[q] = 0.0;
+  double logp = 0.0;
+  for (int64_t i = 0; i < n; ++i) {
+    double mx = -INFINITY;
+    for (int64_t c = 0; c < C; ++c) {                                               /* :82-83 */
+      double s = 0.0;
+      for (int64_t j = 0; j < k; ++j) s += x_at(a, i, j) * a->beta[c * k + j];
+      lin[c] = s + a->alpha[c];
+      if (lin[c] > mx) mx = lin[c];                                                 /* :84-85 */
+    }
+    double sum = 0.0;
+    for (int64_t c = 0; c < C; ++c) { e[c] = exp(lin[c] - mx); sum += e[c]; }       /* :88-91 */
+    const double inv = 1.0 / sum;
+    const int64_t yc = (int64_t)y_at(a, i) - 1;
+    logp += log(inv) - mx + lin[yc];                                                /* :93, :98-104 */
+    for (int64_t c = 0; c < C; ++c) {
+      const double d = (c == yc ? 1.0 : 0.0) - e[c] * inv;                          /* :147-148, :157-159, :172-178 */
+      if (want_da) a->dalpha[c] += d;
+      if (want_db) for (int64_t j = 0; j < k; ++j) a->dbeta[c * k + j] += x_at(a, i, j) * d;
+    }
+  }
+  free(lin);
+  free(e);
+  if (a->lp) *a->lp = (a->flags & STAN_CUDA_LP_MAIN) ? logp : 0.0;
+  if (a->aux) { a->aux[0] = 0; a->aux[1] = logp; a->aux[2] = 0; a->aux[3] = 0; }
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;                         /* :109 */
+}
+
 int oracle_glm_eval(const stan_cuda_glm_args* a) {
   if (!a || a->n < 0 || a->k < 0) return STAN_CUDA_ERR_ARG;
+  if (a->family == STAN_CUDA_CATEGORICAL_LOGIT) {
+    if (a->n_classes < 1 || a->alpha_len != a->n_classes) return STAN_CUDA_ERR_ARG;
+    return categorical_logit_glm(a);
+  }
   if (a->family != STAN_CUDA_ORDERED_LOGISTIC && a->alpha_len != 1 && a->alpha_len != a->n) return STAN_CUDA_ERR_ARG;
   double* d = (double*)calloc((size_t)(a->n > 0 ? a->n : 1), sizeof(double));
   if (!d) return STAN_CUDA_ERR_ARG;

@@ -58,6 +58,9 @@ def ref_lib():
         if hasattr(lib, "stanref_ordered_logistic_glm"):
             lib.stanref_ordered_logistic_glm.restype = i
             lib.stanref_ordered_logistic_glm.argtypes = [i, l, l, dp, vp, dp, dp, l, dp, dp, dp, dp, C.c_char_p, i]
+        if hasattr(lib, "stanref_categorical_logit_glm"):
+            lib.stanref_categorical_logit_glm.restype = i
+            lib.stanref_categorical_logit_glm.argtypes = [i, l, l, l, dp, vp, dp, dp, dp, dp, dp, dp, C.c_char_p, i]
         lib.stanref_glm_value.restype = i
         lib.stanref_glm_value.argtypes = [i, i, l, l, dp, vp, dp, l, dp, dp, l, dp, C.c_char_p, i]
         lib.stanref_normal_lpdf.restype = i
@@ -180,6 +183,31 @@ def oracle_ordered_logistic_glm(x, y, beta, cuts, propto=False, flags=None):
             "dcuts": out["dcuts"][:cuts.size].copy(), "aux": out["aux"].copy()}
 
 
+def _prep_categorical(x, y, alpha, beta):
+    x = np.asfortranarray(np.asarray(x, dtype=np.float64))
+    y = np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+    alpha = _f64(alpha)
+    beta = np.asfortranarray(np.asarray(beta, dtype=np.float64).reshape(x.shape[1], -1))
+    return x, y, alpha, beta
+
+
+def oracle_categorical_logit_glm(x, y, alpha, beta, propto=False, flags=None):
+    """beta: (k, C).  Returns lp, dalpha (C), dbeta (k, C)."""
+    x, y, alpha, beta = _prep_categorical(x, y, alpha, beta)
+    n, k = x.shape
+    ncls = beta.shape[1]
+    lp, dalpha, dbeta, aux = np.zeros(1), np.zeros(max(ncls, 1)), np.zeros((max(k, 1), max(ncls, 1)), order="F"), np.zeros(4)
+    a = _abi.GlmArgs()
+    a.family, a.n, a.k, a.n_classes = _abi.CATEGORICAL_LOGIT, n, k, ncls
+    a.flags = (_abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA) if flags is None else flags
+    a.x, a.ldx, a.x_row_major, a.y, a.y_is_double = x.ctypes.data, max(n, 1), 0, y.ctypes.data, 0
+    a.alpha, a.alpha_len, a.beta = alpha.ctypes.data, alpha.size, beta.ctypes.data
+    a.lp, a.dalpha, a.dbeta, a.aux = lp.ctypes.data, dalpha.ctypes.data, dbeta.ctypes.data, aux.ctypes.data
+    rc = oracle_lib().oracle_glm_eval(C.byref(a))
+    return {"rc": rc, "lp": float(lp[0]), "dalpha": dalpha[:ncls].copy(),
+            "dbeta": np.asarray(dbeta).reshape(-1, order="F")[:k * ncls].reshape((k, ncls), order="F").copy()}
+
+
 class RefError(Exception):
     def __init__(self, rc, msg):
         super().__init__(msg)
@@ -225,6 +253,21 @@ def ref_ordered_logistic_glm(x, y, beta, cuts, propto=False):
         raise RefError(rc, err.value.decode())
     return {"rc": 0, "lp": float(lp[0]), "dbeta": dbeta[:k].copy(), "dcuts": dcuts[:cuts.size].copy(),
             "seconds": float(secs[0])}
+
+
+def ref_categorical_logit_glm(x, y, alpha, beta, propto=False):
+    x, y, alpha, beta = _prep_categorical(x, y, alpha, beta)
+    n, k = x.shape
+    ncls = beta.shape[1]
+    lp, dalpha, dbeta, secs = np.zeros(1), np.zeros(max(ncls, 1)), np.zeros(max(k * ncls, 1)), np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_categorical_logit_glm(int(propto), n, k, ncls, x.ctypes.data, y.ctypes.data,
+                                                 alpha.ctypes.data, beta.ctypes.data, lp.ctypes.data,
+                                                 dalpha.ctypes.data, dbeta.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return {"rc": 0, "lp": float(lp[0]), "dalpha": dalpha[:ncls].copy(),
+            "dbeta": dbeta[:k * ncls].reshape((k, ncls), order="F").copy(), "seconds": float(secs[0])}
 
 
 def ref_glm_value(family, x, y, alpha, beta, sigma=None, propto=False):

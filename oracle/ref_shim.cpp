@@ -16,6 +16,7 @@
 //   normal_lpdf               stan/math/prim/scal/prob/normal_lpdf.hpp:36-112
 //   neg_binomial_2_log_glm_lpmf stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:60-197
 //   ordered_logistic_glm_lpmf stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:46-222
+//   categorical_logit_glm_lpmf stan/math/prim/mat/prob/categorical_logit_glm_lpmf.hpp:38-193
 //   map_rect                  stan/math/prim/mat/functor/map_rect.hpp:120-177
 #include <stan/math.hpp>
 
@@ -173,6 +174,30 @@ int stanref_ordered_logistic_glm(int propto, long n, long k, const double* x, co
         if (lp) *lp = res.val();
         read_adj(beta_v, dbeta);
         read_adj(cuts_v, dcuts);
+      },
+      err, errlen);
+}
+
+// categorical_logit_glm_lpmf(y, x, alpha, beta) with var alpha (C) and beta (k x C, column-major).
+int stanref_categorical_logit_glm(int propto, long n, long k, long n_classes, const double* x, const int* y,
+                                  const double* alpha, const double* beta, double* lp, double* dalpha,
+                                  double* dbeta, double* seconds, char* err, int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d xm = Eigen::Map<const matrix_d>(x, n, k);
+        std::vector<int> yi(y, y + n);
+        vector_v alpha_v = make_vars(alpha, n_classes);
+        Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic> beta_v(k, n_classes);
+        for (long q = 0; q < k * n_classes; ++q) beta_v(q) = beta[q];
+        auto t0 = std::chrono::steady_clock::now();
+        var res = propto ? stan::math::categorical_logit_glm_lpmf<true>(yi, xm, alpha_v, beta_v)
+                         : stan::math::categorical_logit_glm_lpmf<false>(yi, xm, alpha_v, beta_v);
+        res.grad();
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        if (lp) *lp = res.val();
+        read_adj(alpha_v, dalpha);
+        if (dbeta) for (long q = 0; q < k * n_classes; ++q) dbeta[q] = beta_v(q).adj();
       },
       err, errlen);
 }

@@ -14,6 +14,7 @@
 #include <stan/math/cuda/normal_id_glm_lpdf.hpp>
 #include <stan/math/cuda/neg_binomial_2_log_glm_lpmf.hpp>
 #include <stan/math/cuda/ordered_logistic_glm_lpmf.hpp>
+#include <stan/math/cuda/categorical_logit_glm_lpmf.hpp>
 #include <stan/math/cuda/normal_lpdf.hpp>
 #include <stan/math/cuda/map_rect_devices.hpp>
 #endif

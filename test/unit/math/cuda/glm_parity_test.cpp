@@ -206,6 +206,43 @@ TEST(CudaGlmVariants, ordered_logistic) {
   EXPECT_THROW(ordered_logistic_glm_lpmf(y_low, p.x, beta, cuts), std::domain_error);
 }
 
+TEST(CudaGlmVariants, categorical_logit) {
+  using stan::math::categorical_logit_glm_lpmf;
+  using stan::math::categorical_logit_glm_lpmf_reference_cpu;
+  typedef Eigen::Matrix<var, Dynamic, Dynamic> matrix_v;
+  Problem p = make_problem(4001, 29, 12);
+  const int C = 5;
+  std::mt19937_64 rng(77);
+  std::normal_distribution<double> nd(0.0, 0.3);
+  MatrixXd beta_d(29, C);
+  VectorXd alpha_d(C);
+  for (int q = 0; q < beta_d.size(); ++q) beta_d(q) = nd(rng);
+  for (int c = 0; c < C; ++c) alpha_d[c] = nd(rng);
+  std::vector<int> y(p.y_pois.size());
+  for (size_t i = 0; i < y.size(); ++i) y[i] = 1 + (p.y_pois[i] + static_cast<int>(i)) % C;
+  matrix_v beta = beta_d.cast<var>();
+  vector_v alpha = to_v(alpha_d);
+  auto adj_m = [](const matrix_v& m) {
+    VectorXd g(m.size());
+    for (int q = 0; q < m.size(); ++q) g[q] = m(q).adj();
+    return g;
+  };
+  STAN_CUDA_PARITY("categorical_logit", categorical_logit_glm_lpmf(y, p.x, alpha, beta),
+                   categorical_logit_glm_lpmf_reference_cpu(y, p.x, alpha, beta), adj_m(beta), adj(alpha));
+  STAN_CUDA_PARITY("categorical_logit propto, data alpha", categorical_logit_glm_lpmf<true>(y, p.x, alpha_d, beta),
+                   categorical_logit_glm_lpmf_reference_cpu<true>(y, p.x, alpha_d, beta), adj_m(beta));
+  STAN_CUDA_PARITY("categorical_logit data beta", categorical_logit_glm_lpmf(y, p.x, alpha, beta_d),
+                   categorical_logit_glm_lpmf_reference_cpu(y, p.x, alpha, beta_d), adj(alpha));
+  EXPECT_NEAR(categorical_logit_glm_lpmf(y, p.x, alpha_d, beta_d),
+              categorical_logit_glm_lpmf_reference_cpu(y, p.x, alpha_d, beta_d), 1e-8);
+  EXPECT_EQ(categorical_logit_glm_lpmf<true>(y, p.x, alpha_d, beta_d), 0.0);
+  std::vector<int> y_high = y, y_low = y;
+  y_high[17] = C + 1;
+  y_low[17] = 0;
+  EXPECT_THROW(categorical_logit_glm_lpmf(y_high, p.x, alpha, beta), std::domain_error);
+  EXPECT_THROW(categorical_logit_glm_lpmf(y_low, p.x, alpha, beta), std::domain_error);
+}
+
 TEST(CudaGlmVariants, zero_copy_data_view) {
   Problem p = make_problem(4001, 37, 9);
   vector_v beta = to_v(p.beta);

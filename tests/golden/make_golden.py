@@ -165,7 +165,34 @@ for n, k, c, tag in ((153, 71, 4, "big"), (600, 128, 10, "wide"), (1000, 1, 3, "
 x = rng3.standard_normal((64, 2)) * 30
 add_ord("tails", x, rng3.integers(1, 4, 64), [1.0, -1.0], [-1.0, 2.0])
 
+# categorical_logit_glm (key space "cat/"): the fixture of
+# test/unit/math/rev/mat/prob/categorical_logit_glm_lpmf_test.cpp:551-580 (x 5 x 2, beta 2 x 3, alpha (0.5, -2, 4),
+# y = {1, 3, 1, 2, 2}) and random cases up to 16 classes
+cat_names = []
+
+
+def add_cat(name, x, y, alpha, beta, propto=False):
+    r = L.ref_categorical_logit_glm(x, y, alpha, beta, propto=propto)
+    p = "cat/%s/" % name
+    out[p + "x"], out[p + "y"] = np.asarray(x, float), np.asarray(y, np.int32)
+    out[p + "alpha"], out[p + "beta"] = np.atleast_1d(np.asarray(alpha, float)), np.asarray(beta, float)
+    out[p + "propto"] = np.array(int(propto))
+    out[p + "lp"], out[p + "dalpha"], out[p + "dbeta"] = np.array(r["lp"]), r["dalpha"], r["dbeta"]
+    cat_names.append(name)
+
+
+rng4 = np.random.default_rng(20191107)
+XC = np.array([[-12, 46], [-42, 24], [25, 27], [-14, -11], [5, 18]], float)
+BC = np.array([[0.3, 2, 0.4], [-0.1, -1.3, 1]], float)
+add_cat("fixture", XC, [1, 3, 1, 2, 2], [0.5, -2, 4], BC)
+add_cat("fixture_propto", XC, [1, 3, 1, 2, 2], [0.5, -2, 4], BC, propto=True)
+for n, k, c, tag in ((153, 71, 4, "big"), (400, 128, 10, "wide"), (1000, 1, 3, "k1"), (500, 33, 16, "many"), (300, 7, 2, "two")):
+    x = rng4.standard_normal((n, k))
+    beta = rng4.standard_normal((k, c)) * (1.5 / np.sqrt(k))
+    add_cat("rand_" + tag, x, rng4.integers(1, c + 1, n), rng4.standard_normal(c), beta)
+
 out["glm_cases"] = np.array(names)
+out["cat_cases"] = np.array(cat_names)
 out["ord_cases"] = np.array(ord_names)
 out["normal_cases"] = np.array(nl)
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "glm_golden.npz")

@@ -103,3 +103,26 @@ def synth_ordered(n, k, n_classes, seed):
     lat = x @ beta_true + rng.logistic(size=n)
     y = (1 + np.searchsorted(cuts, lat)).astype(np.int32)
     return {"x": x, "y": y, "beta": beta_true + 0.05 * rng.standard_normal(k), "cuts": cuts}
+
+
+def cat_case(golden, name):
+    p = "cat/%s/" % name
+    c = {k: golden[p + k] for k in ("x", "y", "alpha", "beta", "dalpha", "dbeta")}
+    c["lp"], c["propto"] = float(golden[p + "lp"]), bool(golden[p + "propto"])
+    return c
+
+
+def check_cat_result(r, c, what, rtol=RTOL):
+    assert_close(r["lp"], c["lp"], what + " lp", rtol)
+    assert_close(r["dalpha"], c["dalpha"], what + " dalpha", rtol)
+    assert_close(np.asarray(r["dbeta"]).ravel(order="F"), np.asarray(c["dbeta"]).ravel(order="F"), what + " dbeta", rtol)
+
+
+def synth_categorical(n, k, n_classes, seed):
+    rng = np.random.default_rng(seed)
+    x = np.asfortranarray(rng.standard_normal((n, k)))
+    beta_true = rng.standard_normal((k, n_classes)) * (1.0 / np.sqrt(k))
+    alpha = rng.standard_normal(n_classes) * 0.5
+    z = x @ beta_true + alpha + rng.gumbel(size=(n, n_classes))
+    y = (1 + np.argmax(z, axis=1)).astype(np.int32)
+    return {"x": x, "y": y, "alpha": alpha + 0.1, "beta": beta_true + 0.05 * rng.standard_normal((k, n_classes))}

@@ -13,7 +13,7 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CXX_DIR = os.path.join(ROOT, "build", "cxx")
 BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_poisson_log_glm_lpmf_test",
-            "ref_normal_id_glm_lpdf_test", "ref_neg_binomial_2_log_glm_lpmf_test", "ref_ordered_logistic_glm_lpmf_test", "ref_operands_and_partials_test", "ref_precomputed_gradients_test",
+            "ref_normal_id_glm_lpdf_test", "ref_neg_binomial_2_log_glm_lpmf_test", "ref_ordered_logistic_glm_lpmf_test", "ref_categorical_logit_glm_lpmf_test", "ref_operands_and_partials_test", "ref_precomputed_gradients_test",
             "ref_map_rect_concurrent_test"]
 
 

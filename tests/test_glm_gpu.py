@@ -5,8 +5,8 @@ import numpy as np
 import pytest
 
 from math_b200 import _abi
-from tests.helpers import (RTOL, assert_close, check_glm_result, check_ord_result, glm_case, normal_case, ord_case,
-                           synth_glm, synth_ordered)
+from tests.helpers import (RTOL, assert_close, cat_case, check_cat_result, check_glm_result, check_ord_result, glm_case,
+                           normal_case, ord_case, synth_categorical, synth_glm, synth_ordered)
 
 pytestmark = pytest.mark.gpu
 
@@ -110,6 +110,75 @@ def test_ordered_logistic_error_contract(glm):
     with pytest.raises(Exception) as e:
         f([1] * 5, x, beta, np.arange(300.0))
     assert "256" in str(e.value)
+
+
+CAT_FLAGS = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA
+
+
+def test_golden_categorical_logit_cases(glm, golden):
+    for name in golden["cat_cases"]:
+        c = cat_case(golden, str(name))
+        r = glm.categorical_logit_glm_eval(c["y"], c["x"], c["alpha"], c["beta"], CAT_FLAGS)
+        assert r["rc"] == 0, name
+        check_cat_result(r, c, "cuda vs golden cat " + str(name))
+        lp, g = glm.categorical_logit_glm_lpmf(c["y"], c["x"], c["alpha"], c["beta"], propto=c["propto"])
+        assert lp == r["lp"] and np.array_equal(g["beta"], r["dbeta"]) and np.array_equal(g["alpha"], r["dalpha"])
+
+
+# (2000, 500, 6) rather than (2100, 500, 6): at that seed one of the 3000 gradient components cancels to 3e-8 of the
+# largest, and two CPU evaluations (plain-C oracle, compiled reference) already differ by 2e-10 on it
+CAT_SHAPES = [(1, 1, 2), (5, 2, 3), (33, 7, 1), (1000, 16, 4), (4097, 33, 7), (100000, 32, 5), (30011, 128, 10),
+              (9000, 256, 16), (2000, 500, 6), (50000, 8, 16), (3000, 40, 2), (70000, 32, 3)]
+
+
+@pytest.mark.parametrize("n,k,c", CAT_SHAPES)
+def test_categorical_logit_against_oracle(glm, L, n, k, c):
+    s = synth_categorical(n, k, c, seed=13 * n + k + c)
+    ref = L.oracle_categorical_logit_glm(s["x"], s["y"], s["alpha"], s["beta"])
+    got = glm.categorical_logit_glm_eval(s["y"], s["x"], s["alpha"], s["beta"], CAT_FLAGS)
+    assert got["rc"] == ref["rc"] == 0
+    check_cat_result(got, ref, "categorical %dx%d C=%d" % (n, k, c))
+    again = glm.categorical_logit_glm_eval(s["y"], s["x"], s["alpha"], s["beta"], CAT_FLAGS)
+    assert again["lp"] == got["lp"] and np.array_equal(again["dbeta"], got["dbeta"])   # fixed summation order
+    only = glm.categorical_logit_glm_eval(s["y"], s["x"], s["alpha"], s["beta"], _abi.LP_MAIN)
+    assert only["lp"] == got["lp"]
+
+
+def test_categorical_logit_error_contract(glm):
+    """categorical_logit_glm_lpmf_test.cpp:551-620 (glm_errors)."""
+    x = np.array([[-12, 46], [-42, 24], [25, 27], [-14, -11], [5, 18]], float)
+    beta = np.array([[0.3, 2, 0.4], [-0.1, -1.3, 1]], float)
+    y, alpha = [1, 3, 1, 2, 2], [0.5, -2, 4]
+    f = glm.categorical_logit_glm_lpmf
+    f(y, x, alpha, beta)
+
+    def size_error(*args):
+        with pytest.raises(ValueError) as e:
+            f(*args)
+        assert not isinstance(e.value, glm.DomainError)
+
+    size_error([1, 3, 1, 2, 2, 1], x, alpha, beta)
+    size_error(y, np.vstack([x, [[1, 2]]]), alpha, beta)
+    size_error(y, np.hstack([x, x[:, :1]]), alpha, beta)
+    size_error(y, x, [0.5, -2, 4, 3], beta)
+    size_error(y, x, alpha, np.vstack([beta, beta[:1]]))
+    size_error(y, x, alpha, np.hstack([beta, beta[:, :1]]))
+    for bad_y in ([1, 3, 1, 2, 4], [1, 3, 1, 2, 0]):
+        with pytest.raises(glm.DomainError):
+            f(bad_y, x, alpha, beta)
+    for bad in (np.nan, np.inf):
+        xv, bv, av = x.copy(), beta.copy(), np.array(alpha, float)
+        xv[4, 1], bv[1, 2], av[2] = bad, bad, bad
+        with pytest.raises(glm.DomainError):
+            f(y, xv, alpha, beta)
+        with pytest.raises(glm.DomainError):
+            f(y, x, alpha, bv)
+        with pytest.raises(glm.DomainError):
+            f(y, x, av, beta)
+    assert f([1] * 5, x, [0.3], beta[:, :1])[0] == 0.0      # single class (:66-68)
+    with pytest.raises(Exception) as e:                      # beyond the device limit: loud, no fallback
+        f([1] * 5, x, np.zeros(17), np.zeros((2, 17)))
+    assert "16" in str(e.value)
 
 
 def test_golden_normal_cases(glm, golden):

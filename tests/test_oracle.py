@@ -4,8 +4,8 @@ import numpy as np
 import pytest
 
 from oracle import loader as L
-from tests.helpers import (assert_close, check_glm_result, check_ord_result, glm_case, normal_case, ord_case,
-                           synth_glm, synth_ordered)
+from tests.helpers import (assert_close, cat_case, check_cat_result, check_glm_result, check_ord_result, glm_case,
+                           normal_case, ord_case, synth_categorical, synth_glm, synth_ordered)
 from math_b200 import _abi
 
 
@@ -29,6 +29,15 @@ def test_oracle_ordered_logistic_matches_golden(golden):
         r = L.oracle_ordered_logistic_glm(c["x"], c["y"], c["beta"], c["cuts"], propto=c["propto"])
         assert r["rc"] == 0, name
         check_ord_result(r, c, "oracle vs golden ord " + str(name), rtol=1e-11)
+
+
+def test_oracle_categorical_logit_matches_golden(golden):
+    assert len(golden["cat_cases"]) >= 7
+    for name in golden["cat_cases"]:
+        c = cat_case(golden, str(name))
+        r = L.oracle_categorical_logit_glm(c["x"], c["y"], c["alpha"], c["beta"], propto=c["propto"])
+        assert r["rc"] == 0, name
+        check_cat_result(r, c, "oracle vs golden cat " + str(name), rtol=1e-11)
 
 
 def test_oracle_normal_matches_golden_and_known_answers(golden):
@@ -87,6 +96,15 @@ def test_oracle_ordered_logistic_vs_compiled_reference(n, k, c):
     ref = L.ref_ordered_logistic_glm(s["x"], s["y"], s["beta"], s["cuts"])
     got = L.oracle_ordered_logistic_glm(s["x"], s["y"], s["beta"], s["cuts"])
     check_ord_result(got, ref, "ordered %dx%d C=%d" % (n, k, c), rtol=1e-11)
+
+
+@needs_ref
+@pytest.mark.parametrize("n,k,c", [(1, 1, 2), (50, 3, 1), (500, 32, 5), (900, 130, 12)])
+def test_oracle_categorical_logit_vs_compiled_reference(n, k, c):
+    s = synth_categorical(n, k, c, seed=n + 7 * k + c)
+    ref = L.ref_categorical_logit_glm(s["x"], s["y"], s["alpha"], s["beta"])
+    got = L.oracle_categorical_logit_glm(s["x"], s["y"], s["alpha"], s["beta"])
+    check_cat_result(got, ref, "categorical %dx%d C=%d" % (n, k, c), rtol=1e-11)
 
 
 @needs_ref
