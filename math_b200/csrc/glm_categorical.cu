@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(kCatThreads, 2) glm_categorical_kernel(const G
 
   unsigned char* stage0 = smem;
   double* bs = reinterpret_cast<double*>(smem + size_t(p.stages) * p.stage_bytes);  // [ncls][bstride]
-  double* alpha_s = bs + size_t(ncls) * bstride;                                     // [ncls]
+  double* alpha_s = bs + size_t(ncls) * bstride + kMaxKc;                            // [ncls] (16 zeros behind bs)
   double* lin = alpha_s + ncls;                                                      // [R][ls]
   double* part = lin + size_t(R) * ls;                                               // [NT] (lp partials), first 8 reused
   uint64_t* full = reinterpret_cast<uint64_t*>(part + NT);                           // [stages]
@@ -58,6 +58,8 @@ __global__ void __launch_bounds__(kCatThreads, 2) glm_categorical_kernel(const G
     mbar_fence_init();
   }
   // weights (class-major rows of k_pad in the parameter block) and intercepts into shared memory
+  for (int q = tid; q < ncls * bstride + kMaxKc; q += NT) bs[q] = 0.0;
+  __syncthreads();
   for (int q = tid; q < ncls * kpad; q += NT) {
     const int c = q / kpad, k = q - c * kpad;
     bs[size_t(c) * bstride + (k / kc) * (kc + 1) + (k % kc)] = p.params[q];
@@ -102,49 +104,45 @@ __global__ void __launch_bounds__(kCatThreads, 2) glm_categorical_kernel(const G
     mbar_wait(smem_u32(&full[s]), (it / p.stages) & 1);
     const unsigned char* st = stage0 + size_t(s) * p.stage_bytes;
     const double* xt = reinterpret_cast<const double*>(st);
-    // ---- A: lin = x * beta + alpha for the rows of this warp ------------------------------------
+    // ---- A + S inside the warp: lin = x * beta + alpha for the rows of this warp, then the softmax of
+    // each row split over the C lanes that share it (lane cg takes classes cg, cg + C, ...) --------------
     {
       const double* xs = xt + warp * 32 + lane;
       double xr[kMaxKc];
 #pragma unroll
       for (int j = 0; j < kMaxKc; ++j) xr[j] = j < kc ? xs[j * NT] : 0.0;
       const double* bl = bs + cg * (kc + 1);
+      double* l = lin + r_own * ls;
+      const int64_t row = tile * R + r_own;
+      const bool valid = row < p.n;
+      const int yc = valid ? reinterpret_cast<const int*>(st + p.tile_bytes)[r_own] - 1 : 0;  // 1 <= y <= ncls: checked at fill
+      double mx = -__longlong_as_double(0x7ff0000000000000LL), ly = 0.0;
       for (int c = 0; c < ncls; ++c) {
         const double* b = bl + size_t(c) * bstride;
         double p0 = 0.0, p1 = 0.0;
 #pragma unroll
-        for (int j = 0; j < kMaxKc; j += 2) {
-          if (j < kc) p0 = fma(xr[j], b[j], p0);
-          if (j + 1 < kc) p1 = fma(xr[j + 1], b[j + 1], p1);
+        for (int j = 0; j < kMaxKc; j += 2) {  // j >= kc: x is 0 and b reads zero padding (or a finite neighbour)
+          p0 = fma(xr[j], b[j], p0);
+          p1 = fma(xr[j + 1], b[j + 1], p1);
         }
         double v = p0 + p1;
         for (int off = 1; off < C; off <<= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-        if (cg == 0) lin[r_own * ls + c] = v + alpha_s[c];
+        v += alpha_s[c];
+        mx = fmax(mx, v);                                                            // :84-85 (every lane of the row)
+        if (c == yc) ly = v;
+        if (cg == (c & (C - 1))) l[c] = v;
       }
-    }
-    __syncthreads();
-    // ---- S: softmax of one row per thread, in place: lin <- onehot(y) - softmax(lin) -------------
-    if (tid < R) {
-      const int64_t row = tile * R + tid;
-      const bool valid = row < p.n;
-      double* l = lin + tid * ls;
-      if (valid) {
-        const int yc = reinterpret_cast<const int*>(st + p.tile_bytes)[tid] - 1;  // 1 <= y <= ncls: checked at fill
-        double mx = l[0];
-        for (int c = 1; c < ncls; ++c) mx = fmax(mx, l[c]);                       // :84-85
-        const double ly = l[yc];
-        double sum = 0.0;
-        for (int c = 0; c < ncls; ++c) {                                          // :88-89
-          const double e = exp(l[c] - mx);
-          l[c] = e;
-          sum += e;
-        }
-        const double inv = 1.0 / sum;                                             // :90-91
-        lp_acc += log(inv) - mx + ly;                                             // :93, :98-104
-        for (int c = 0; c < ncls; ++c) l[c] = (c == yc ? 1.0 : 0.0) - l[c] * inv; // :147-148 (+ onehot, :157-159, :172-178)
-      } else {
-        for (int c = 0; c < ncls; ++c) l[c] = 0.0;
+      double sum = 0.0;
+      for (int c = cg; c < ncls; c += C) {                                           // :88-89
+        const double e = exp(l[c] - mx);  // this lane wrote l[c] itself and is the only one to touch it
+        sum += e;
+        l[c] = e;
       }
+      for (int off = 1; off < C; off <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+      const double inv = 1.0 / sum;                                                  // :90-91
+      if (valid && cg == 0) lp_acc += log(inv) - mx + ly;                            // :93, :98-104
+      for (int c = cg; c < ncls; c += C)
+        l[c] = valid ? ((c == yc ? 1.0 : 0.0) - l[c] * inv) : 0.0;                   // :147-148 + onehot (:157-159, :172-178)
     }
     __syncthreads();
     // ---- B: gradient x' * d, classes of group g, x slices of row group q0 --------------------------
@@ -199,7 +197,7 @@ __global__ void __launch_bounds__(kCatThreads, 2) glm_categorical_kernel(const G
   double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
   if (tid == 0) {
     double sum = 0.0;
-    for (int t = 0; t < R && t < NT; ++t) sum += part[t];
+    for (int t = 0; t < NT; ++t) sum += part[t];
     my_scratch[0] = sum;
     my_scratch[1] = 0.0;
     my_scratch[2] = 0.0;
@@ -224,7 +222,7 @@ static inline size_t align_up_cat(size_t v, size_t a) { return (v + a - 1) / a *
 static size_t cat_smem_bytes(const Tiling& t, int stages, int ncls, size_t* stage_bytes_out) {
   const size_t stage = align_up_cat(t.tile_bytes() + size_t(t.R) * sizeof(double), 128);
   if (stage_bytes_out) *stage_bytes_out = stage;
-  const size_t doubles = size_t(ncls) * t.C * (t.kc + 1) + ncls + size_t(t.R) * (ncls | 1) + kCatThreads;
+  const size_t doubles = size_t(ncls) * t.C * (t.kc + 1) + kMaxKc + ncls + size_t(t.R) * (ncls | 1) + kCatThreads;
   return size_t(stages) * stage + doubles * sizeof(double) + size_t(stages) * sizeof(uint64_t) + 16;
 }
 

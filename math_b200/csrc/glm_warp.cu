@@ -31,13 +31,15 @@ constexpr int kWarpThreads = kWarpConsumers * 32;
 
 __device__ __forceinline__ void consumer_sync() { __syncthreads(); }
 
-template <int FAMILY, bool ROWIO>
+// FULLKC: every column group has all kMaxKc columns (k_pad is a multiple of 16, the case whenever K >= 16):
+// the `j < kc` guards of the register loops vanish at compile time.
+template <int FAMILY, bool ROWIO, bool FULLKC>
 __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKernelParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr int NT = kWarpConsumers * 32;
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  const int C = p.C, kc = p.kc, kpad = p.kpad, R = p.R;
+  const int C = p.C, kc = FULLKC ? kMaxKc : p.kc, kpad = p.kpad, R = p.R;
   const int rpw = 32 / C;  // rows per warp
   const int cg = lane & (C - 1);
   const int rl = lane / C;
@@ -287,9 +289,9 @@ static size_t warp_smem_bytes(const Tiling& t, int stages, int ncuts, size_t* st
   return size_t(stages) * stage + fixed;
 }
 
-template <int FAMILY, bool ROWIO>
-static int launch_warp_inst(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
-  auto kern = glm_warp_kernel<FAMILY, ROWIO>;
+template <int FAMILY, bool ROWIO, bool FULLKC>
+static int launch_warp_inst2(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
+  auto kern = glm_warp_kernel<FAMILY, ROWIO, FULLKC>;
   static std::atomic<size_t> configured[64];
   int dev = 0;
   SC_CUDA(cudaGetDevice(&dev));
@@ -301,6 +303,15 @@ static int launch_warp_inst(const GlmKernelParams& p, int grid, size_t smem, cud
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
+}
+
+template <int FAMILY, bool ROWIO>
+static int launch_warp_inst(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
+  // measured: the specialisation gains 1-4 % for the cheap epilogues; for neg_binomial_2_log it costs registers
+  // (more spills, 208 -> 242 us at 1.25e6 x 128), so that family stays on the generic instantiation
+  if (FAMILY != STAN_CUDA_NEG_BINOMIAL_2_LOG && p.kc == kMaxKc)
+    return launch_warp_inst2<FAMILY, ROWIO, FAMILY != STAN_CUDA_NEG_BINOMIAL_2_LOG>(p, grid, smem, stream);
+  return launch_warp_inst2<FAMILY, ROWIO, false>(p, grid, smem, stream);
 }
 
 // neg_binomial_2_log with a scalar phi: sum_i lgamma(y_i + phi) and sum_i digamma(y_i + phi) depend on

@@ -73,7 +73,9 @@ def widened(args, torch, glm, peak, stream):
     from math_b200 import _abi
     cases = [("neg_binomial_2_log", 1_250_000, 128, 0), ("neg_binomial_2_log", 1_000_000, 32, 0),
              ("ordered_logistic", 1_250_000, 128, 5), ("ordered_logistic", 1_000_000, 32, 5),
-             ("ordered_logistic", 1_000_000, 32, 64)]
+             ("ordered_logistic", 1_000_000, 32, 64), ("categorical_logit", 1_250_000, 128, 4),
+             ("categorical_logit", 1_000_000, 32, 4), ("categorical_logit", 1_000_000, 32, 3),
+             ("categorical_logit", 1_000_000, 32, 16)]
     for family, n, k, ncls in cases:
         x, y, alpha, beta, _ = synth_shard("poisson_log", n, k, seed=1)
         fam = _abi.FAMILIES[family]
@@ -84,15 +86,28 @@ def widened(args, torch, glm, peak, stream):
             flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
         else:
             flags = glm.glm_flags(fam, False)
+        cat = fam == _abi.CATEGORICAL_LOGIT
+        if cat:
+            y = (1 + (y + np.arange(n)) % ncls).astype(np.int32)
+            flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA
         data = glm.GlmData(fam, x, y)
-        params = np.zeros(data.params_len + ncuts)
-        params[:k], params[data.kpad], params[data.kpad + 1] = beta, alpha[0], 2.5
-        params[data.kpad + 2:] = np.linspace(-1.5, 1.5, ncuts)
+        if cat:
+            params = np.zeros(ncls * (data.kpad + 1))
+            for c in range(ncls):
+                params[c * data.kpad:c * data.kpad + k] = beta * (1 + 0.1 * c)
+            params[ncls * data.kpad:] = np.linspace(-0.5, 0.5, ncls)
+            dr = torch.zeros(4 + ncls * (data.kpad + 1), dtype=torch.float64, device="cuda")
+        else:
+            params = np.zeros(data.params_len + ncuts)
+            params[:k], params[data.kpad], params[data.kpad + 1] = beta, alpha[0], 2.5
+            params[data.kpad + 2:] = np.linspace(-1.5, 1.5, ncuts)
+            dr = torch.zeros(data.result_len + ncuts, dtype=torch.float64, device="cuda")
         dp = torch.from_numpy(params).cuda()
-        dr = torch.zeros(data.result_len + ncuts, dtype=torch.float64, device="cuda")
 
         def go():
-            if ncuts:
+            if cat:
+                data.launch_categorical(flags, dp.data_ptr(), ncls, dr.data_ptr(), stream.cuda_stream)
+            elif ncuts:
                 data.launch_ordered(flags, dp.data_ptr(), ncuts, dr.data_ptr(), stream.cuda_stream)
             else:
                 data.launch(flags, dp.data_ptr(), dr.data_ptr(), stream.cuda_stream)

@@ -1,4 +1,4 @@
-"""One shape, three launches of the GLM kernel: the target of `ncu --set full -k regex:glm_warp_kernel -s 2 -c 1`.
+"""One shape, three launches of the GLM kernel: the target of `ncu --set full -k regex:glm_ -s 2 -c 1`.
 usage: ncu_one.py FAMILY N K warp|cta [CLASSES]"""
 import os
 import sys
@@ -22,16 +22,28 @@ flags = glm.glm_flags(fam, False) if fam != _abi.ORDERED_LOGISTIC else (_abi.LP_
 if fam == _abi.ORDERED_LOGISTIC:
     y = (1 + (y + np.arange(n)) % ncls).astype(np.int32)
     ncuts = ncls - 1
+cat = fam == _abi.CATEGORICAL_LOGIT
+if cat:
+    y = (1 + (y + np.arange(n)) % ncls).astype(np.int32)
+    flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA
 data = glm.GlmData(fam, x, y)
 params = np.zeros(data.params_len + ncuts)
 params[:k], params[data.kpad] = beta, alpha[0]
 params[data.kpad + 1] = 2.5 if fam == _abi.NEG_BINOMIAL_2_LOG else 1.0
 params[data.kpad + 2:] = np.linspace(-1.5, 1.5, ncuts)
-dp = torch.from_numpy(params).cuda()
 dr = torch.zeros(data.result_len + ncuts, dtype=torch.float64, device="cuda")
+if cat:
+    params = np.zeros(ncls * (data.kpad + 1))
+    for c in range(ncls):
+        params[c * data.kpad:c * data.kpad + k] = beta * (1 + 0.1 * c)
+    params[ncls * data.kpad:] = np.linspace(-0.5, 0.5, ncls)
+    dr = torch.zeros(4 + ncls * (data.kpad + 1), dtype=torch.float64, device="cuda")
+dp = torch.from_numpy(params).cuda()
 s = torch.cuda.Stream()
 for _ in range(3):
-    if ncuts:
+    if cat:
+        data.launch_categorical(flags, dp.data_ptr(), ncls, dr.data_ptr(), s.cuda_stream)
+    elif ncuts:
         data.launch_ordered(flags, dp.data_ptr(), ncuts, dr.data_ptr(), s.cuda_stream)
     else:
         data.launch(flags, dp.data_ptr(), dr.data_ptr(), s.cuda_stream)
