@@ -35,6 +35,7 @@ struct GlmKernelParams {
   int nb_rowfun;          // neg_binomial_2_log: per-row lgamma/digamma (vector phi or no histogram)
   int ncuts;              // ordered_logistic: number of cut-points (classes - 1); 0 otherwise
   int ncls, cat_groups;   // categorical_logit: classes; class groups of the gradient phase (glm_categorical.cu)
+  int pair;               // warp kernel: two tiles per iteration (glm_warp.cu, PAIR)
   int ord_private;        // ordered_logistic: d/dcuts bins private to each row slot of the tile ([ncuts][R] in shared memory)
   // low-latency host path: parameters by value, completion flag in mapped host memory
   int inline_n;                        // > 0: read the parameter block from inline_params

@@ -33,7 +33,10 @@ __device__ __forceinline__ void consumer_sync() { __syncthreads(); }
 
 // FULLKC: every column group has all kMaxKc columns (k_pad is a multiple of 16, the case whenever K >= 16):
 // the `j < kc` guards of the register loops vanish at compile time.
-template <int FAMILY, bool ROWIO, bool FULLKC>
+// PAIR (needs FULLKC and C >= 2): two tiles per iteration; the even column-group lanes of a row evaluate
+// the epilogue of tile A's row, the odd ones tile B's, `d` is exchanged by shuffle and x is re-read from
+// the still-resident stages for the gradient FMAs -- the epilogue runs C/2 instead of C times per row.
+template <int FAMILY, bool ROWIO, bool FULLKC, bool PAIR>
 __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKernelParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr int NT = kWarpConsumers * 32;
@@ -53,7 +56,8 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   const int ord_doubles = FAMILY == STAN_CUDA_ORDERED_LOGISTIC ? kOrdTabRows * (ncuts + 1) : 0;
   const bool ord_private = FAMILY == STAN_CUDA_ORDERED_LOGISTIC && p.ord_private;
   double* ord_bins = ord_tab + ord_doubles;                                          // [ncuts][R] when ord_private
-  uint64_t* full = reinterpret_cast<uint64_t*>(ord_bins + (ord_private ? ncuts * R : 0));  // [stages]
+  const int RS = PAIR ? 2 * R : R;  // row slots of d/dcuts bins (PAIR: tile A slots, then tile B slots)
+  uint64_t* full = reinterpret_cast<uint64_t*>(ord_bins + (ord_private ? ncuts * RS : 0));  // [stages]
   int* arrived = reinterpret_cast<int*>(full + p.stages);                            // [stages]
   __shared__ int s_flag;
 
@@ -83,7 +87,7 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
     ordered_class_table<NT>(p, ord_tab, tid);
     for (int j = tid; j < kWarpConsumers * ncuts; j += NT) red[size_t(j / ncuts) * cols + kpad + 4 + j % ncuts] = 0.0;
     if (ord_private)
-      for (int j = tid; j < ncuts * R; j += NT) ord_bins[j] = 0.0;
+      for (int j = tid; j < ncuts * RS; j += NT) ord_bins[j] = 0.0;
   }
   __syncthreads();
 
@@ -122,51 +126,11 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // lp main, sum d, sum s^2, sum log sigma (cg == 0 lanes)
   const int r_in_tile = warp * rpw + rl;
 
-  for (int it = 0; it < ntl; ++it) {
-    const int s = it % p.stages;
-    const int64_t tile = tile0 + int64_t(it) * tstride;
-    const int64_t row = tile * R + r_in_tile;
-    mbar_wait(smem_u32(&full[s]), (it / p.stages) & 1);
-#ifdef STAN_CUDA_PHASE_TIMERS
-    if (it == 0) PHASE_STAMP(1);
-    if (p.timers && (it & 7) == 0 && (it >> 3) < 32 && lane == 0 && (warp == 0 || warp == 7))
-      p.timers[8 * 2048 + (size_t(blockIdx.x) * 2 + (warp == 7)) * 32 + (it >> 3)] = gtimer();
-#endif
-    const unsigned char* st = stage0 + size_t(s) * p.stage_bytes;
-    const double* xs = reinterpret_cast<const double*>(st) + warp * 32 + lane;
-    double xr[kMaxKc];
-#pragma unroll
-    for (int j = 0; j < kMaxKc; ++j) xr[j] = j < kc ? xs[j * NT] : 0.0;
-    double yv;
-    if (FAMILY == STAN_CUDA_NORMAL_ID) {  // the only family with real-valued outcomes
-      yv = reinterpret_cast<const double*>(st + p.tile_bytes)[r_in_tile];
-    } else {
-      yv = double(reinterpret_cast<const int*>(st + p.tile_bytes)[r_in_tile]);
-    }
-
-    double p0 = 0.0, p1 = 0.0;
-#pragma unroll
-    for (int j = 0; j < kMaxKc; j += 2) {
-      p0 = fma(xr[j], bj[j], p0);
-      p1 = fma(xr[j + 1], bj[j + 1], p1);
-    }
-    double eta = p0 + p1;
-    // this warp's part of the tile sits in registers: count it; the last warp re-arms the stage
-    __syncwarp();
-    if (lane == 0) {
-      __threadfence_block();
-      if (atomicAdd(&arrived[s], 1) == kWarpConsumers - 1) {
-        arrived[s] = 0;  // the next arrivals on this stage come only after the refill below has landed
-        __threadfence_block();
-        if (it + p.stages < ntl) issue(it + p.stages);
-      }
-    }
-
-    // partial dots of the C column groups of a row: xor butterfly, identical result in every lane
-    for (int off = 1; off < C; off <<= 1) eta += __shfl_xor_sync(0xffffffffu, eta, off);
-
+  // One row's family epilogue: per-row operands, log-density terms and d = dL/deta; the owner lane of
+  // the row (`own`) adds the terms to its accumulators and writes the per-row outputs.  `slot` is the
+  // row's slot in the d/dcuts bins, `u` the PAIR role (0: tile A, 1: tile B; always 0 otherwise).
+  auto row_terms = [&](double eta, double yv, int64_t row, bool valid, bool own, int slot, int u) -> double {
     double alpha = alpha0, inv_sigma = inv_sigma0, sigma_row = sigma0, log_sigma_row = log_sigma0;
-    const bool valid = row < p.n;
     if (ROWIO && valid) {
       if (p.alpha_vec) alpha = p.alpha_vec[row];
       if (FAMILY >= STAN_CUDA_NORMAL_ID && p.sigma_vec) {
@@ -179,7 +143,7 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
     if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
       const int c = valid ? int(yv) : 1;  // 1 <= c <= ncuts + 1 was checked from the range of y cached at fill
       o = ordered_row_epilogue(eta, c, ncuts + 1, ord_tab);
-      if (valid && cg == 0) {
+      if (valid && own) {
         a0 += o.t0;
         a1 += o.d;
         a2 += eta;  // ordered_logistic_glm_lpmf.hpp:119: finiteness of sum(location)
@@ -187,16 +151,16 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
       if ((p.flags & STAN_CUDA_NEED_DCUTS) && ord_private) {
         // d/dcuts (:192-200), few classes: every row slot of the tile owns a private row of bins
         // ([class][row slot]: conflict-free, no ordering question), summed in slot order at the end
-        if (valid && cg == 0) {
-          if (c != ncuts + 1) ord_bins[(c - 1) * R + r_in_tile] += o.t3;
-          if (c != 1) ord_bins[(c - 2) * R + r_in_tile] -= o.t2;
+        if (valid && own) {
+          if (c != ncuts + 1) ord_bins[(c - 1) * RS + slot] += o.t3;
+          if (c != 1) ord_bins[(c - 2) * RS + slot] -= o.t2;
         }
       } else if ((p.flags & STAN_CUDA_NEED_DCUTS) && ncuts > 0) {
         // many classes: one owner lane per row adds into this warp's bins, rows in order, so the sum is
         // the same on every run (no floating-point atomics)
         double* bins = red + size_t(warp) * cols + kpad + 4;
-        for (int r = 0; r < rpw; ++r) {
-          if (rl == r && cg == 0 && valid) {
+        for (int r = 0; r < (PAIR ? 2 : 1) * rpw; ++r) {
+          if (rl == (PAIR ? r >> 1 : r) && (!PAIR || u == (r & 1)) && own && valid) {
             if (c != ncuts + 1) bins[c - 1] += o.t3;
             if (c != 1) bins[c - 2] -= o.t2;
           }
@@ -208,8 +172,7 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
     } else {
       o = row_epilogue<FAMILY>(eta, alpha, yv, inv_sigma);
     }
-    const double d = valid ? o.d : 0.0;
-    if (FAMILY != STAN_CUDA_ORDERED_LOGISTIC && valid && cg == 0) {
+    if (FAMILY != STAN_CUDA_ORDERED_LOGISTIC && valid && own) {
       a0 += o.t0;
       a1 += o.d;
       a2 += o.t2;
@@ -224,8 +187,115 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
         if (p.row_dalpha) p.row_dalpha[row] = o.d;
       }
     }
+    return valid ? o.d : 0.0;
+  };
+  // this warp is done with stage s (tile number `it` of the CTA): count it; the last warp re-arms the stage
+  auto release = [&](int s, int it) {
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence_block();
+      if (atomicAdd(&arrived[s], 1) == kWarpConsumers - 1) {
+        arrived[s] = 0;  // the next arrivals on this stage come only after the refill below has landed
+        __threadfence_block();
+        if (it + p.stages < ntl) issue(it + p.stages);
+      }
+    }
+  };
+  auto outcome = [&](const unsigned char* st) -> double {
+    if (FAMILY == STAN_CUDA_NORMAL_ID) return reinterpret_cast<const double*>(st + p.tile_bytes)[r_in_tile];
+    return double(reinterpret_cast<const int*>(st + p.tile_bytes)[r_in_tile]);
+  };
+
+  if (PAIR) {
+    const int u = cg & 1;  // this lane's role: epilogue of tile A's row (0) or of tile B's row (1)
+    for (int it = 0; it < ntl; it += 2) {
+      const bool have_b = it + 1 < ntl;
+      const int sa = it % p.stages, sb = (it + 1) % p.stages;
+      const unsigned char* sta = stage0 + size_t(sa) * p.stage_bytes;
+      const unsigned char* stb = stage0 + size_t(sb) * p.stage_bytes;
+      const double* xa = reinterpret_cast<const double*>(sta) + warp * 32 + lane;
+      const double* xb = reinterpret_cast<const double*>(stb) + warp * 32 + lane;
+      double eta_a, eta_b = 0.0, y_a, y_b = 0.0;
+      mbar_wait(smem_u32(&full[sa]), (it / p.stages) & 1);
+#ifdef STAN_CUDA_PHASE_TIMERS
+      if (it == 0) PHASE_STAMP(1);
+#endif
+      {
+        double p0 = 0.0, p1 = 0.0;
 #pragma unroll
-    for (int j = 0; j < kMaxKc; ++j) acc[j] = fma(xr[j], d, acc[j]);
+        for (int j = 0; j < kMaxKc; j += 2) {
+          p0 = fma(xa[j * NT], bj[j], p0);
+          p1 = fma(xa[(j + 1) * NT], bj[j + 1], p1);
+        }
+        eta_a = p0 + p1;
+        y_a = outcome(sta);
+      }
+      if (have_b) {
+        mbar_wait(smem_u32(&full[sb]), ((it + 1) / p.stages) & 1);
+        double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+        for (int j = 0; j < kMaxKc; j += 2) {
+          p0 = fma(xb[j * NT], bj[j], p0);
+          p1 = fma(xb[(j + 1) * NT], bj[j + 1], p1);
+        }
+        eta_b = p0 + p1;
+        y_b = outcome(stb);
+      }
+      for (int off = 1; off < C; off <<= 1) {
+        eta_a += __shfl_xor_sync(0xffffffffu, eta_a, off);
+        eta_b += __shfl_xor_sync(0xffffffffu, eta_b, off);
+      }
+      const int64_t tile = tile0 + int64_t(it + u) * tstride;
+      const int64_t row = tile * R + r_in_tile;
+      const bool valid = row < p.n && (u == 0 || have_b);
+      const double d_mine = row_terms(u ? eta_b : eta_a, u ? y_b : y_a, row, valid, cg == u, r_in_tile + u * R, u);
+      const double d_a = __shfl_sync(0xffffffffu, d_mine, lane & ~1);
+      const double d_b = __shfl_sync(0xffffffffu, d_mine, lane | 1);
+#pragma unroll
+      for (int j = 0; j < kMaxKc; ++j) acc[j] = fma(xa[j * NT], d_a, acc[j]);
+      release(sa, it);
+      if (have_b) {
+#pragma unroll
+        for (int j = 0; j < kMaxKc; ++j) acc[j] = fma(xb[j * NT], d_b, acc[j]);
+        release(sb, it + 1);
+      }
+    }
+    // the owners of tile B rows (cg == 1) hand their sums to the cg == 0 lanes; other lanes hold zeros
+    a0 += __shfl_xor_sync(0xffffffffu, a0, 1);
+    a1 += __shfl_xor_sync(0xffffffffu, a1, 1);
+    a2 += __shfl_xor_sync(0xffffffffu, a2, 1);
+    a3 += __shfl_xor_sync(0xffffffffu, a3, 1);
+  } else {
+    for (int it = 0; it < ntl; ++it) {
+      const int s = it % p.stages;
+      const int64_t tile = tile0 + int64_t(it) * tstride;
+      const int64_t row = tile * R + r_in_tile;
+      mbar_wait(smem_u32(&full[s]), (it / p.stages) & 1);
+#ifdef STAN_CUDA_PHASE_TIMERS
+      if (it == 0) PHASE_STAMP(1);
+      if (p.timers && (it & 7) == 0 && (it >> 3) < 32 && lane == 0 && (warp == 0 || warp == 7))
+        p.timers[8 * 2048 + (size_t(blockIdx.x) * 2 + (warp == 7)) * 32 + (it >> 3)] = gtimer();
+#endif
+      const unsigned char* st = stage0 + size_t(s) * p.stage_bytes;
+      const double* xs = reinterpret_cast<const double*>(st) + warp * 32 + lane;
+      double xr[kMaxKc];
+#pragma unroll
+      for (int j = 0; j < kMaxKc; ++j) xr[j] = j < kc ? xs[j * NT] : 0.0;
+      const double yv = outcome(st);
+      double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+      for (int j = 0; j < kMaxKc; j += 2) {
+        p0 = fma(xr[j], bj[j], p0);
+        p1 = fma(xr[j + 1], bj[j + 1], p1);
+      }
+      double eta = p0 + p1;
+      release(s, it);  // this warp's part of the tile sits in registers
+      // partial dots of the C column groups of a row: xor butterfly, identical result in every lane
+      for (int off = 1; off < C; off <<= 1) eta += __shfl_xor_sync(0xffffffffu, eta, off);
+      const double d = row_terms(eta, yv, row, row < p.n, cg == 0, r_in_tile, 0);
+#pragma unroll
+      for (int j = 0; j < kMaxKc; ++j) acc[j] = fma(xr[j], d, acc[j]);
+    }
   }
 
   PHASE_STAMP(2);
@@ -263,8 +333,8 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   for (int c = tid; c < cols; c += NT) {
     double sum = 0.0;
     if (ord_private && c >= kpad + 4) {
-      const double* b = ord_bins + (c - kpad - 4) * R;
-      for (int r = 0; r < R; ++r) sum += b[r];
+      const double* b = ord_bins + (c - kpad - 4) * RS;
+      for (int r = 0; r < RS; ++r) sum += b[r];
     } else {
 #pragma unroll
       for (int w = 0; w < kWarpConsumers; ++w) sum += red[size_t(w) * cols + c];
@@ -280,18 +350,27 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
 // =============================================================================================
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-static bool ord_private_bins(const Tiling& t, int ncuts) { return ncuts > 0 && size_t(ncuts) * t.R <= size_t(kOrdPrivateDoubles); }
+static bool pair_mode(const Tiling& t) {
+  static const int on = [] {
+    const char* v = getenv("STAN_CUDA_PAIR");  // STAN_CUDA_PAIR=0: one tile per iteration (A/B)
+    return v ? atoi(v) : 1;
+  }();
+  return on != 0 && t.kc == kMaxKc && t.C >= 2;
+}
+static bool ord_private_bins(const Tiling& t, int ncuts) {
+  return ncuts > 0 && size_t(ncuts) * t.R * (pair_mode(t) ? 2 : 1) <= size_t(kOrdPrivateDoubles);
+}
 
 static size_t warp_smem_bytes(const Tiling& t, int stages, int ncuts, size_t* stage_bytes_out) {
   const size_t stage = align_up(t.tile_bytes() + size_t(t.R) * sizeof(double), 128);
   if (stage_bytes_out) *stage_bytes_out = stage;
-  const size_t fixed = (size_t(kWarpConsumers) * (t.kpad + 4 + ncuts) + 8 + size_t(kOrdTabRows) * (ncuts + 1) + (ord_private_bins(t, ncuts) ? size_t(ncuts) * t.R : 0)) * sizeof(double) + size_t(stages) * (sizeof(uint64_t) + sizeof(int)) + 8;
+  const size_t fixed = (size_t(kWarpConsumers) * (t.kpad + 4 + ncuts) + 8 + size_t(kOrdTabRows) * (ncuts + 1) + (ord_private_bins(t, ncuts) ? size_t(ncuts) * t.R * (pair_mode(t) ? 2 : 1) : 0)) * sizeof(double) + size_t(stages) * (sizeof(uint64_t) + sizeof(int)) + 8;
   return size_t(stages) * stage + fixed;
 }
 
-template <int FAMILY, bool ROWIO, bool FULLKC>
+template <int FAMILY, bool ROWIO, bool FULLKC, bool PAIR = false>
 static int launch_warp_inst2(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
-  auto kern = glm_warp_kernel<FAMILY, ROWIO, FULLKC>;
+  auto kern = glm_warp_kernel<FAMILY, ROWIO, FULLKC, PAIR>;
   static std::atomic<size_t> configured[64];
   int dev = 0;
   SC_CUDA(cudaGetDevice(&dev));
@@ -309,6 +388,7 @@ template <int FAMILY, bool ROWIO>
 static int launch_warp_inst(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
   // measured: the specialisation gains 1-4 % for the cheap epilogues; for neg_binomial_2_log it costs registers
   // (more spills, 208 -> 242 us at 1.25e6 x 128), so that family stays on the generic instantiation
+  if (p.pair) return launch_warp_inst2<FAMILY, ROWIO, true, true>(p, grid, smem, stream);
   if (FAMILY != STAN_CUDA_NEG_BINOMIAL_2_LOG && p.kc == kMaxKc)
     return launch_warp_inst2<FAMILY, ROWIO, FAMILY != STAN_CUDA_NEG_BINOMIAL_2_LOG>(p, grid, smem, stream);
   return launch_warp_inst2<FAMILY, ROWIO, false>(p, grid, smem, stream);
@@ -400,6 +480,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   p.stage_bytes = uint32_t(stage_bytes);
   p.blocked = tuning().blocked;
   p.ord_private = ord_private_bins(t, ncuts) ? 1 : 0;
+  p.pair = pair_mode(t) && stages >= 3 ? 1 : 0;
   const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
   switch (d->family) {
     case STAN_CUDA_BERNOULLI_LOGIT:
