@@ -9,7 +9,8 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from tests.helpers import check_glm_result, synth_glm  # noqa: E402
+from tests.helpers import (check_cat_result, check_glm_result, check_ord_result, synth_categorical, synth_glm,  # noqa: E402
+                           synth_ordered)
 
 
 def in_process_row_sharding_with_nccl(family):
@@ -40,6 +41,41 @@ def in_process_row_sharding_with_nccl(family):
     glm.cache_clear()
 
 
+def widened_families_row_sharded():
+    """neg_binomial_2_log, ordered_logistic (result block with d/dcuts: fused exchange) and categorical_logit
+    (result block wider than an exchange slot: ncclAllReduce behind the kernels) across the devices."""
+    from math_b200 import _abi, glm
+    from math_b200._lib import lib
+    from oracle import loader as L
+    glm.init(0)
+    assert lib().stan_cuda_device_count() >= 2
+    lib().stan_cuda_set_shard_min_elems(1 << 16)
+    n, k = 150_001, 48
+    s = synth_glm("neg_binomial_2_log", n, k, seed=23)
+    ref = L.oracle_glm("neg_binomial_2_log", s["x"], s["y"], s["alpha"], s["beta"], s["sigma"])
+    got = glm.glm_eval("neg_binomial_2_log", s["y"], s["x"], s["alpha"], s["beta"], s["sigma"])
+    check_glm_result(got, ref, "sharded neg_binomial_2_log")
+    so = synth_ordered(n, k, 6, seed=29)
+    flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+    st0 = glm.stats()
+    got = glm.ordered_logistic_glm_eval(so["y"], so["x"], so["beta"], so["cuts"], flags)
+    st1 = glm.stats()
+    check_ord_result(got, L.oracle_ordered_logistic_glm(so["x"], so["y"], so["beta"], so["cuts"]), "sharded ordered_logistic")
+    assert st1["kernel_launches"] - st0["kernel_launches"] >= 2
+    for ncls in (3, 16):   # 16 classes x k_pad 48: 788 doubles > one exchange slot
+        sc = synth_categorical(n, k, ncls, seed=31 + ncls)
+        st0 = glm.stats()
+        got = glm.categorical_logit_glm_eval(sc["y"], sc["x"], sc["alpha"], sc["beta"],
+                                             _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA)
+        st1 = glm.stats()
+        check_cat_result(got, L.oracle_categorical_logit_glm(sc["x"], sc["y"], sc["alpha"], sc["beta"]),
+                         "sharded categorical_logit C=%d" % ncls)
+        assert (st1["allreduces"] + st1["fused_allreduces"]) - (st0["allreduces"] + st0["fused_allreduces"]) == 1
+        print("categorical C=%d: nccl %d fused %d" % (ncls, st1["allreduces"] - st0["allreduces"],
+                                                      st1["fused_allreduces"] - st0["fused_allreduces"]))
+    glm.cache_clear()
+
+
 def shard_scopes_use_distinct_devices():
     from math_b200 import glm
     from oracle import loader as L
@@ -57,6 +93,8 @@ if __name__ == "__main__":
     case = sys.argv[1]
     if case == "sharding":
         in_process_row_sharding_with_nccl(sys.argv[2])
+    elif case == "widened":
+        widened_families_row_sharded()
     elif case == "scopes":
         shard_scopes_use_distinct_devices()
     else:

@@ -30,6 +30,10 @@ def test_in_process_row_sharding(family):
     _run("sharding", family)
 
 
+def test_widened_families_row_sharded():
+    _run("widened")
+
+
 def test_shard_scopes_use_distinct_devices():
     _run("scopes")
 
