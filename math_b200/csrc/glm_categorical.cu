@@ -117,20 +117,34 @@ __global__ void __launch_bounds__(kCatThreads, 2) glm_categorical_kernel(const G
       const bool valid = row < p.n;
       const int yc = valid ? reinterpret_cast<const int*>(st + p.tile_bytes)[r_own] - 1 : 0;  // 1 <= y <= ncls: checked at fill
       double mx = -__longlong_as_double(0x7ff0000000000000LL), ly = 0.0;
-      for (int c = 0; c < ncls; ++c) {
-        const double* b = bl + size_t(c) * bstride;
-        double p0 = 0.0, p1 = 0.0;
+      // two classes per trip: their dot products are independent chains (the class loop is latency-bound)
+      for (int c = 0; c < ncls; c += 2) {
+        const bool two = c + 1 < ncls;
+        const double* b0 = bl + size_t(c) * bstride;
+        const double* b1 = two ? b0 + bstride : b0;
+        double p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0;
 #pragma unroll
         for (int j = 0; j < kMaxKc; j += 2) {  // j >= kc: x is 0 and b reads zero padding (or a finite neighbour)
-          p0 = fma(xr[j], b[j], p0);
-          p1 = fma(xr[j + 1], b[j + 1], p1);
+          p0 = fma(xr[j], b0[j], p0);
+          q0 = fma(xr[j], b1[j], q0);
+          p1 = fma(xr[j + 1], b0[j + 1], p1);
+          q1 = fma(xr[j + 1], b1[j + 1], q1);
         }
-        double v = p0 + p1;
-        for (int off = 1; off < C; off <<= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+        double v = p0 + p1, w = q0 + q1;
+        for (int off = 1; off < C; off <<= 1) {
+          v += __shfl_xor_sync(0xffffffffu, v, off);
+          w += __shfl_xor_sync(0xffffffffu, w, off);
+        }
         v += alpha_s[c];
         mx = fmax(mx, v);                                                            // :84-85 (every lane of the row)
         if (c == yc) ly = v;
         if (cg == (c & (C - 1))) l[c] = v;
+        if (two) {
+          w += alpha_s[c + 1];
+          mx = fmax(mx, w);
+          if (c + 1 == yc) ly = w;
+          if (cg == ((c + 1) & (C - 1))) l[c + 1] = w;
+        }
       }
       double sum = 0.0;
       for (int c = cg; c < ncls; c += C) {                                           // :88-89
