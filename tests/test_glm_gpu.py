@@ -381,6 +381,51 @@ def test_large_shape_row_additivity(glm, L):
     glm.cache_clear()
 
 
+def _raw_eval(glm, fam, x, ldx, n, k, y, alpha, beta):
+    """stan_cuda_glm_eval on a row block of a column-major matrix, zero-copy (x points at the block's first
+    row, ldx is the full matrix's row count)."""
+    import ctypes as C
+    from math_b200._lib import check, lib
+    a = _abi.GlmArgs()
+    lp, dbeta, dalpha = np.zeros(1), np.zeros(k), np.zeros(1)
+    al, be = np.array([alpha], float), np.ascontiguousarray(beta, dtype=np.float64)
+    a.family, a.n, a.k = fam, n, k
+    a.flags = glm.glm_flags(fam, False)
+    a.x, a.ldx, a.x_row_major = x, ldx, 0
+    a.y, a.y_is_double = y, 0
+    a.alpha, a.alpha_len, a.beta = al.ctypes.data, 1, be.ctypes.data
+    a.lp, a.dbeta, a.dalpha = lp.ctypes.data, dbeta.ctypes.data, dalpha.ctypes.data
+    assert check(lib().stan_cuda_glm_eval(C.byref(a))) == 0
+    return float(lp[0]), dbeta, float(dalpha[0])
+
+
+def test_full_size_c3_row_additivity_and_sample_parity(glm, L, request):
+    """BASELINE configs[2] at its full size (N = 1e7, K = 128, 10.28 GB): value and gradient are sums over rows,
+    so the evaluation of the whole matrix must equal the sum over three uneven row blocks (passed zero-copy
+    through ldx); rows sampled across the whole range are checked against the oracle."""
+    import torch
+    from bench import synth_shard
+    if request.node.callspec.params.get("glm") != "warp":
+        pytest.skip("full size once, on the default kernel")
+    if torch.cuda.mem_get_info()[0] < 40e9:
+        pytest.skip("needs 40 GB of free device memory")
+    n, k = 10_000_000, 128
+    x, y, alpha, beta, _ = synth_shard("poisson_log", n, k, seed=1003)
+    full = _raw_eval(glm, _abi.POISSON_LOG, x.ctypes.data, n, n, k, y.ctypes.data, alpha[0], beta)
+    cuts = [0, 3_333_337, 3_333_337 + 4_096_001, n]
+    parts = [_raw_eval(glm, _abi.POISSON_LOG, x.ctypes.data + 8 * r0, n, r1 - r0, k, y.ctypes.data + 4 * r0, alpha[0], beta)
+             for r0, r1 in zip(cuts[:-1], cuts[1:])]
+    assert_close(sum(p[0] for p in parts), full[0], "C3 additivity lp", 1e-12)
+    assert_close(sum(p[1] for p in parts), full[1], "C3 additivity dbeta", 1e-11)
+    assert_close(sum(p[2] for p in parts), full[2], "C3 additivity dalpha", 1e-11)
+    idx = np.random.default_rng(5).choice(n, 20000, replace=False)
+    xs, ys = np.asfortranarray(x[idx]), np.ascontiguousarray(y[idx])
+    ref = L.oracle_glm("poisson_log", xs, ys, alpha, beta)
+    got = glm.glm_eval("poisson_log", ys, xs, alpha, beta)
+    check_glm_result(got, ref, "rows sampled from C3")
+    glm.cache_clear()
+
+
 def test_device_level_launch_matches_host_level(glm):
     import torch
     s = synth_glm("normal_id", 60000, 64, seed=8)
