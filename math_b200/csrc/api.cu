@@ -324,6 +324,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     LaunchIO io{a->flags, run.d_params, run.d_alpha, run.d_sigma, run.d_result, run.d_rowa, run.d_rows};
     io.ncuts = int(ncuts);
     io.ncls = int(ncls);
+    io.shared_gpu = tl_scope.active;
     if (xchg) {
       io.xchg = S > 1 ? &xchg[s] : xchg;
       io.xchg_seq = xchg_seq;

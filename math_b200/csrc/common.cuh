@@ -114,6 +114,7 @@ struct LaunchIO {
   // categorical_logit: d_params = [beta: ncls rows of kpad (class-major), alpha(ncls)],
   // d_result = [lp, 0, 0, status, dalpha(ncls), dbeta: ncls rows of kpad]
   int ncls = 0;
+  bool shared_gpu = false;  // other launches are expected to run concurrently on this device (map_rect shard scope)
 };
 constexpr int kMaxClasses = 16;              // categorical_logit: classes on the device path
 constexpr int kMaxClassWeights = 4096;       // categorical_logit: classes * k_pad (weights live in shared memory)

@@ -466,6 +466,18 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
 
   int64_t grid64 = int64_t(sms) * ctas_per_sm;
   if (grid64 > t.tiles) grid64 = t.tiles;
+  // Launches that run next to each other (map_rect shards on the streams of concurrent host threads, io.shared_gpu)
+  // take a slice of the SMs each, with enough tiles per CTA to amortise ramp and tail: kernels of different
+  // shards then overlap instead of queueing behind each other's full-width grids.
+  static const int shared_tiles_per_cta = [] {
+    const char* v = getenv("STAN_CUDA_SHARED_TILES_PER_CTA");  // 0: full-width grids; measured at C5: 8 is best
+    return v ? atoi(v) : 8;
+  }();
+  if (io.shared_gpu && shared_tiles_per_cta > 0) {
+    int64_t g = (t.tiles + shared_tiles_per_cta - 1) / shared_tiles_per_cta;
+    if (g < 8) g = 8;
+    if (g < grid64) grid64 = g;
+  }
   const int grid = int(grid64);
   int group_size = 1;
   while (group_size * group_size < grid) ++group_size;
