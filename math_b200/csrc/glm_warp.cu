@@ -20,8 +20,15 @@
 //    in glm_fused.cu one owner warp per CTA ran the epilogue while the other seven sat at a barrier.
 //  * tile layout in HBM (see data.cu): x_dev[tile][j][warp][lane], so the j-th load of a warp is one
 //    contiguous 256-byte shared-memory read, conflict-free.
+//  * two tiles per iteration when a row is shared by C >= 2 lanes (PAIR, below): each row's epilogue is
+//    evaluated by half of its lanes instead of all of them, and x is re-read from the still-resident
+//    stage for the gradient FMAs instead of being held in registers (a stage is then released after
+//    the gradient, not after the load).
 //  * reductions are fixed-order (shuffle trees, then warps in order, then finish_reduction):
 //    results are bit-reproducible.
+// Families: bernoulli_logit, poisson_log, normal_id, neg_binomial_2_log
+// (neg_binomial_2_log_glm_lpmf.hpp:108-197) and ordered_logistic (ordered_logistic_glm_lpmf.hpp:93-199);
+// categorical_logit has its own kernel (glm_categorical.cu).
 #include "glm_device.cuh"
 
 namespace stancuda {
