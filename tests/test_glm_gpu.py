@@ -209,9 +209,11 @@ def test_against_oracle(glm, L, family, n, k):
         check_glm_result(got, ref, "%s %dx%d propto=%s" % (family, n, k, propto))
 
 
+# 150001 rows: every CTA gets several tiles, so the two-tiles-per-iteration loop runs with per-row operands too
+@pytest.mark.parametrize("n", [5003, 150001])
 @pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id", "neg_binomial_2_log"])
-def test_vector_alpha_sigma_and_dy(glm, L, family):
-    n, k = 5003, 40
+def test_vector_alpha_sigma_and_dy(glm, L, family, n):
+    k = 40
     s = synth_glm(family, n, k, seed=99)
     rng = np.random.default_rng(3)
     alpha = 0.3 + 0.1 * rng.standard_normal(n)
