@@ -97,6 +97,7 @@ PROTOTYPES = {
     "stan_cuda_set_shard_min_elems": (None, [C.c_int64]),
     "stan_cuda_set_tuning": (None, [C.c_int, C.c_int, C.c_int]),
     "stan_cuda_set_kernel": (None, [C.c_int]),
+    "stan_cuda_set_categorical_kernel": (None, [C.c_int]),
     "stan_cuda_glm_eval": (C.c_int, [C.POINTER(GlmArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
     "stan_cuda_host_staging": (C.c_void_p, [C.c_size_t]),

@@ -117,7 +117,7 @@ static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* ou
     key = Key(1, uintptr_t(tl_scope.call_id), uintptr_t(tl_scope.job), a->n, a->k, a->family, tl_scope.device);
   } else {
     key = Key(0, uintptr_t(a->x), uintptr_t(a->y), a->n, a->k, a->ldx,
-              int64_t(a->family) * 4 + a->x_row_major * 2 + a->y_is_double);
+              int64_t(a->family) * 4 + a->x_row_major * 2 + a->y_is_double + 64 * tuning().layout + 256 * tuning().cat_mma);
   }
   const uint64_t fp = fingerprint_glm(a);
   std::lock_guard<std::mutex> lk(g_cache_mu);

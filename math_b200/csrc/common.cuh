@@ -43,8 +43,12 @@ constexpr int kMaxKc = 16;
 //               rows per warp rpw = 32 / C, R = 8 * rpw, element (r, col) of a tile with
 //               w = r / rpw, rl = r % rpw, cg = col / kc, j = col % kc lives at
 //               x_dev[tile * kpad * R + (j * 8 + w) * 32 + rl * C + cg]
+//   kLayoutMma  (glm_categorical_mma.cu) fragments of 8 rows x 4 columns in the lane order of the FP64
+//               mma.m8n8k4 A operand; kpad = 8 * ceil(k / 8), R = 64 (kpad <= 64) or 32:
+//               x_dev[tile * kpad * R + ((r / 8) * (kpad / 4) + col / 4) * 32 + (r % 8) * 4 + col % 4]
 constexpr int kLayoutCta = 0;
 constexpr int kLayoutWarp = 1;
+constexpr int kLayoutMma = 2;
 
 struct Tiling {
   int layout;   // kLayoutCta | kLayoutWarp
@@ -126,6 +130,7 @@ constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sig
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 // width of the result block (and of every partial) of one launch
 inline size_t result_cols(const stan_cuda_data* d, const LaunchIO& io) {
   if (d->family == STAN_CUDA_CATEGORICAL_LOGIT) return size_t(4) + size_t(io.ncls) * (d->t.kpad + 1);
@@ -134,7 +139,7 @@ inline size_t result_cols(const stan_cuda_data* d, const LaunchIO& io) {
 int sm_count(int device);
 
 // tuning knobs (env STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM; 0 = auto)
-struct Tuning { int threads = 0, stages = 0, ctas_per_sm = 0, layout = kLayoutWarp, blocked = 0; };
+struct Tuning { int threads = 0, stages = 0, ctas_per_sm = 0, layout = kLayoutWarp, blocked = 0, cat_mma = 0; };
 const Tuning& tuning();
 
 // relayout kernels (data.cu)

@@ -20,6 +20,7 @@ struct TileMap {
 };
 __device__ __forceinline__ int64_t tile_elem_offset(const TileMap& m, int r, int col) {
   if (m.layout == kLayoutCta) return int64_t(col) * m.R + r;
+  if (m.layout == kLayoutMma) return (int64_t(r >> 3) * (m.kpad >> 2) + (col >> 2)) * 32 + (r & 7) * 4 + (col & 3);
   const int rpw = 32 / m.C;
   const int w = r / rpw, rl = r - w * rpw;
   const int cg = col / m.kc, j = col - cg * m.kc;
@@ -254,8 +255,11 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
   d->n = n_rows;
   d->k = k;
   d->y_is_double = y_is_double;
-  // neg_binomial_2_log exists on the warp kernel only
-  if (!choose_tiling(n_rows, k, 0, &d->t, family >= STAN_CUDA_NEG_BINOMIAL_2_LOG ? kLayoutWarp : -1)) {
+  // neg_binomial_2_log and ordered_logistic exist on the warp kernel only; categorical_logit has its own two
+  // kernels: FP64 tensor-core (fragment layout, k <= 256) or vector (warp layout)
+  int force = family >= STAN_CUDA_NEG_BINOMIAL_2_LOG ? kLayoutWarp : -1;
+  if (family == STAN_CUDA_CATEGORICAL_LOGIT && tuning().cat_mma && k <= 256) force = kLayoutMma;
+  if (!choose_tiling(n_rows, k, 0, &d->t, force)) {
     delete d;
     return fail(STAN_CUDA_ERR_ARG, "data block: k > 512 is outside the fused kernel's range");
   }

@@ -235,6 +235,8 @@ static Tuning& tuning_mut() {
     u.blocked = (sv && (sv[0] == 'b' || sv[0] == 'B')) ? 1 : 0;
     const char* kv = getenv("STAN_CUDA_KERNEL");
     u.layout = (kv && (kv[0] == 'c' || kv[0] == 'C')) ? kLayoutCta : kLayoutWarp;
+    const char* cv = getenv("STAN_CUDA_CATEGORICAL");
+    u.cat_mma = (cv && (cv[0] == 'm' || cv[0] == 'M')) ? 1 : 0;
     return u;
   }();
   return t;
@@ -256,6 +258,18 @@ int sm_count(int device) {
 bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t, int force_layout) {
   if (k < 1) k = 1;
   const int layout = force_layout >= 0 ? force_layout : tuning().layout;
+  if (layout == kLayoutMma) {
+    // fragments of 8 rows x 4 columns (glm_categorical_mma.cu); tiles of at most 32 KiB up to 64 columns
+    if (k > 256) return false;
+    t->layout = kLayoutMma;
+    t->threads = 256;
+    t->kpad = int((k + 7) / 8) * 8;
+    t->C = 1;
+    t->kc = t->kpad;
+    t->R = t->kpad <= 64 ? 64 : 32;
+    t->tiles = (n + t->R - 1) / t->R;
+    return true;
+  }
   if (layout == kLayoutWarp) {
     // 8 consumer warps of 32 lanes; smallest power-of-two C <= 32 with at most kMaxKc columns per lane
     int C = 1;
@@ -399,7 +413,8 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
 
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
-  if (d->family == STAN_CUDA_CATEGORICAL_LOGIT) return launch_glm_categorical(d, io, ws, stream);
+  if (d->family == STAN_CUDA_CATEGORICAL_LOGIT)
+    return t.layout == kLayoutMma ? launch_glm_categorical_mma(d, io, ws, stream) : launch_glm_categorical(d, io, ws, stream);
   if (t.layout == kLayoutWarp) return launch_glm_warp(d, io, ws, stream);
   if (d->family >= STAN_CUDA_NEG_BINOMIAL_2_LOG)
     return fail(STAN_CUDA_ERR_ARG, "launch_glm: neg_binomial_2_log and ordered_logistic run on the warp kernel only");
@@ -456,6 +471,8 @@ extern "C" STAN_CUDA_API void stan_cuda_debug_set_timers(unsigned long long* dev
 extern "C" void stan_cuda_set_kernel(int variant) {
   stancuda::tuning_mut().layout = variant == 0 ? stancuda::kLayoutCta : stancuda::kLayoutWarp;
 }
+
+extern "C" void stan_cuda_set_categorical_kernel(int variant) { stancuda::tuning_mut().cat_mma = variant == 1 ? 1 : 0; }
 
 extern "C" void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm) {
   stancuda::Tuning& t = stancuda::tuning_mut();

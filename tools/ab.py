@@ -24,6 +24,8 @@ def main():
     ap.add_argument("--ctas", type=int, default=0)
     ap.add_argument("--shapes", default="")
     ap.add_argument("--widened", action="store_true", help="neg_binomial_2_log and ordered_logistic shapes instead")
+    ap.add_argument("--cat-kernel", default="warp", help="categorical_logit kernel: warp (vector FP64) | mma (DMMA)")
+    ap.add_argument("--only", default="", help="--widened: only the families whose name contains this")
     args = ap.parse_args()
     import torch
     from bench import FAM_ID, measured_peak, synth_shard
@@ -76,7 +78,14 @@ def widened(args, torch, glm, peak, stream):
              ("ordered_logistic", 1_000_000, 32, 64), ("categorical_logit", 1_250_000, 128, 4),
              ("categorical_logit", 1_000_000, 32, 4), ("categorical_logit", 1_000_000, 32, 3),
              ("categorical_logit", 1_000_000, 32, 16)]
+    from math_b200._lib import lib
+    lib().stan_cuda_set_categorical_kernel(1 if args.cat_kernel == "mma" else 0)
+    if args.cat_kernel == "mma":
+        cases += [("categorical_logit", 1_250_000, 128, 16), ("categorical_logit", 1_000_000, 64, 8),
+                  ("categorical_logit", 500_000, 256, 16)]
     for family, n, k, ncls in cases:
+        if args.only and args.only not in family:
+            continue
         x, y, alpha, beta, _ = synth_shard("poisson_log", n, k, seed=1)
         fam = _abi.FAMILIES[family]
         ncuts = 0
@@ -122,7 +131,7 @@ def widened(args, torch, glm, peak, stream):
         stream.synchronize()
         ms = e0.elapsed_time(e1) / args.reps
         gbs = data.algorithmic_bytes / (ms * 1e-3) / 1e9
-        print(json.dumps({"kernel": "warp", "family": family, "n": n, "k": k, "classes": ncls, "us": round(ms * 1e3, 2),
+        print(json.dumps({"kernel": args.cat_kernel if cat else "warp", "family": family, "n": n, "k": k, "classes": ncls, "us": round(ms * 1e3, 2),
                           "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "lp": float(dr[0]),
                           "launches_per_eval": 2 if (fam == _abi.NEG_BINOMIAL_2_LOG) else 1}), flush=True)
         data.close()
