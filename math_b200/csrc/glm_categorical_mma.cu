@@ -49,20 +49,42 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                : "d"(a), "d"(b));
 }
 
+// exp(x) for x <= 0 (softmax terms exp(lin - max)), lean: x = n ln2 + r with |r| <= ln2 / 2, Taylor polynomial of
+// degree 13 in r (remainder below 5e-18), 2^n by an add into the exponent field.  Coefficients come from
+// the constant bank as DFMA operands: the libdevice exp spends more instructions on materialising its
+// constants and on the range checks this argument range does not need than on arithmetic (ncu: 64 % of the
+// kernel's instructions were the softmax phase).  x < -708 (a result below 1e-307 next to a sum >= 1) gives 0.
+__constant__ double kExpTaylor[14] = {1.0, 1.0, 1.0 / 2, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
+                                      1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600, 1.0 / 6227020800.0};
+__device__ __forceinline__ double exp_nonpos(double x) {
+  const double t = fma(x, 1.4426950408889634074, 6755399441055744.0);  // low word of t = rint(x / ln2)
+  const int n = __double2loint(t);
+  const double fn = t - 6755399441055744.0;
+  double r = fma(fn, -6.93147180369123816490e-01, x);  // ln2 split in two (fdlibm)
+  r = fma(fn, -1.90821492927058770002e-10, r);
+  double p = kExpTaylor[13];
+#pragma unroll
+  for (int i = 12; i >= 0; --i) p = fma(p, r, kExpTaylor[i]);
+  const double v = __hiloint2double(__double2hiint(p) + n * 1048576, __double2loint(p));
+  return x != x ? x : (x < -708.0 ? 0.0 : v);  // NaN (inf - inf) stays NaN: the caller's finiteness witness sees it
+}
+
 // NTL: n-tiles of 8 classes (1 | 2).  MPW: m-tiles of 8 columns per warp in phase B (1 | 2 | 4).
-template <int NTL, int MPW>
+// TPR: threads per row in phase S (4: 64 rows per tile, 8: 32 rows).  CPT: classes per thread in phase S,
+// ceil(classes / TPR).  All four are functions of (k_pad, classes); eight combinations exist (launch below).
+template <int NTL, int MPW, int TPR, int CPT>
 __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(const GlmKernelParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr int NT = kMmaThreads;
   constexpr int ldl = NTL == 1 ? 8 : 24;  // row stride of the partial lin block (== 8 mod 16: conflict-free C-fragment stores)
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  const int kpad = p.kpad, R = p.R, ncls = p.ncls;
-  const int kb = kpad >> 2;   // k-blocks of 4 columns
-  const int MT = kpad >> 3;   // m-tiles of 8 columns
-  const int RB = R >> 3;      // row blocks: 8 (R = 64) or 4 (R = 32)
-  const int KS = 8 / RB;      // warps per row block in phase A (1 | 2), each a slice of the k-blocks
-  const int TPR = NT / R;     // threads per row in phase S (4 | 8)
+  constexpr int R = NT / TPR;  // rows per tile: 64 | 32
+  constexpr int RB = R >> 3;   // row blocks: 8 | 4
+  constexpr int KS = 8 / RB;   // warps per row block in phase A (1 | 2), each a slice of the k-blocks
+  const int kpad = p.kpad, ncls = p.ncls;
+  const int kb = kpad >> 2;    // k-blocks of 4 columns
+  const int MT = kpad >> 3;    // m-tiles of 8 columns
   const int cols = 4 + ncls + ncls * kpad;
 
   unsigned char* stage0 = smem;
@@ -118,7 +140,7 @@ __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(con
   const bool want_grad = (p.flags & (STAN_CUDA_NEED_DBETA | STAN_CUDA_NEED_DALPHA)) != 0;
   // phase A: row block and k-slice of this warp
   const int rbk = warp % RB, ks = warp / RB;
-  const int kbeg = ks * (kb / KS), kend = (ks == KS - 1) ? kb : kbeg + kb / KS;
+  const int kbeg = ks * (kb / KS), kend = (ks == KS - 1) ? kb : kbeg + kb / KS;  // (kb is even)
   // phase S: row and class lane of this thread (class q, q + TPR, ...; at most 4 of them)
   const int srow = tid / TPR, sq = tid % TPR;
   // phase B: m-tiles mt0, mt0 + 8, ... of this warp; with fewer than 8 m-tiles the warps also split the rows
@@ -142,8 +164,13 @@ __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(con
   for (int m = 0; m < MPW; ++m)
 #pragma unroll
     for (int j = 0; j < NTL; ++j) g[m][j][0] = g[m][j][1] = 0.0;
-  double da[4] = {0.0, 0.0, 0.0, 0.0};
+  double da[CPT];
+#pragma unroll
+  for (int i = 0; i < CPT; ++i) da[i] = 0.0;
   double lp_acc = 0.0;
+  // sum_rows log(1 / sum_c exp(.)) = -log(prod_rows sum_c exp(.)): the sums lie in [1, 16], so a running product of up
+  // to 128 of them (< 2^512) replaces 128 logarithms by one
+  double prod = 1.0;
   const double neg_inf = -__longlong_as_double(0x7ff0000000000000LL);
 
   for (int it = 0; it < ntl; ++it) {
@@ -154,25 +181,25 @@ __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(con
     const double* xt = reinterpret_cast<const double*>(st);
     // ---- A: partial lin of row block rbk over the k-blocks [kbeg, kend) -------------------------------
     {
-      const double* xa = xt + size_t(rbk) * kb * 32 + lane;
-      const double* bf = bfrag + lane;
+      const double* xa = xt + (size_t(rbk) * kb + kbeg) * 32 + lane;
+      const double* bf = bfrag + size_t(kbeg) * NTL * 32 + lane;
       double c[NTL][2][2];  // [n-tile][chain][2]: two independent accumulation chains per n-tile
 #pragma unroll
       for (int j = 0; j < NTL; ++j) c[j][0][0] = c[j][0][1] = c[j][1][0] = c[j][1][1] = 0.0;
-      int kblk = kbeg;
-      for (; kblk + 1 < kend; kblk += 2) {
-        const double a0 = xa[kblk * 32], a1 = xa[(kblk + 1) * 32];
+      int left = kend - kbeg;
+#pragma unroll 2
+      for (; left >= 2; left -= 2, xa += 64, bf += 2 * NTL * 32) {
+        const double a0 = xa[0], a1 = xa[32];
 #pragma unroll
         for (int j = 0; j < NTL; ++j) {
-          const double b0 = bf[(kblk * NTL + j) * 32], b1 = bf[((kblk + 1) * NTL + j) * 32];
-          dmma884(c[j][0][0], c[j][0][1], a0, b0);
-          dmma884(c[j][1][0], c[j][1][1], a1, b1);
+          dmma884(c[j][0][0], c[j][0][1], a0, bf[j * 32]);
+          dmma884(c[j][1][0], c[j][1][1], a1, bf[(NTL + j) * 32]);
         }
       }
-      if (kblk < kend) {
-        const double a0 = xa[kblk * 32];
+      if (left) {
+        const double a0 = xa[0];
 #pragma unroll
-        for (int j = 0; j < NTL; ++j) dmma884(c[j][0][0], c[j][0][1], a0, bf[(kblk * NTL + j) * 32]);
+        for (int j = 0; j < NTL; ++j) dmma884(c[j][0][0], c[j][0][1], a0, bf[j * 32]);
       }
       double* lrow = linp + size_t(ks * R + rbk * 8 + (lane >> 2)) * ldl + 2 * (lane & 3);
 #pragma unroll
@@ -181,50 +208,58 @@ __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(con
     }
     __syncthreads();  // partial lin complete; every warp is past phase B of the previous tile
     if (tid == 0 && it >= 1 && it - 1 + p.stages < ntl) issue(it - 1 + p.stages);  // refill the previous tile's stage
-    // ---- S: softmax of row srow, classes sq, sq + TPR, ... ---------------------------------------------
+    // ---- S: softmax of row srow, classes sq, sq + TPR, ... (branch-free: a slot without a class carries -inf,
+    // its exponential is 0 and its d is 0, written into the zero padding of the d fragment) ---------------
     {
-      const int64_t row = tile * R + srow;
-      const bool valid = row < p.n;
+      const int64_t left_rows = p.n - tile * R;
+      const bool valid = srow < (left_rows < R ? int(left_rows) : R);
       const int yc = valid ? reinterpret_cast<const int*>(st + p.tile_bytes)[srow] - 1 : -1;  // 1 <= y <= ncls: checked at fill
-      double v[4];
-      double mx = neg_inf;
+      double v[CPT];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int c = sq + TPR * i;
-        v[i] = 0.0;
-        if (c < ncls) {
-          double t = linp[size_t(srow) * ldl + c];
-          if (KS == 2) t += linp[size_t(R + srow) * ldl + c];
-          v[i] = t + alpha_s[c];
-          mx = fmax(mx, v[i]);                                                       // :84-85
-        }
+      for (int i = 0; i < CPT; ++i) {
+        const int c = sq + TPR * i;  // < 8 * NTL: inside the (zero padded) row of linp
+        double t = linp[srow * ldl + c];
+        if (KS == 2) t += linp[(R + srow) * ldl + c];
+        t += alpha_s[c];
+        v[i] = (i < CPT - 1 || c < ncls) ? t : neg_inf;
       }
-      for (int off = 1; off < TPR; off <<= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+      double mx = v[0];                                                              // :84-85
+#pragma unroll
+      for (int i = 1; i < CPT; ++i) mx = v[i] > mx ? v[i] : mx;
+#pragma unroll
+      for (int off = 1; off < TPR; off <<= 1) {
+        const double o = __shfl_xor_sync(0xffffffffu, mx, off);
+        mx = o > mx ? o : mx;
+      }
       double sum = 0.0, ly = 0.0;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int c = sq + TPR * i;
-        if (c < ncls) {
-          if (c == yc) ly = v[i];
-          v[i] = exp(v[i] - mx);                                                     // :88-89
-          sum += v[i];
-        }
+      for (int i = 0; i < CPT; ++i) {
+        ly = (sq + TPR * i == yc) ? v[i] : ly;
+        v[i] = exp_nonpos(v[i] - mx);                                                // :88-89
+        sum += v[i];
       }
+#pragma unroll
       for (int off = 1; off < TPR; off <<= 1) {
         sum += __shfl_xor_sync(0xffffffffu, sum, off);
         ly += __shfl_xor_sync(0xffffffffu, ly, off);
       }
       const double inv = 1.0 / sum;                                                  // :90-91
-      if (valid && sq == 0) lp_acc += log(inv) - mx + ly;                            // :93, :98-104
+      if (valid && sq == 0) {                                                        // :93, :98-104: log(inv) - mx + ly
+        lp_acc += ly - mx;
+        prod *= sum;
+      }
+      if ((it & 127) == 127) {
+        lp_acc -= log(prod);
+        prod = 1.0;
+      }
+      // B fragment of phase B: rows are the contraction index (row % 4), classes the n index (c % 8)
+      double* drow = dfrag + (srow >> 2) * (NTL * 32) + (srow & 3);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
+      for (int i = 0; i < CPT; ++i) {
         const int c = sq + TPR * i;
-        if (c < ncls) {
-          const double dv = valid ? ((c == yc ? 1.0 : 0.0) - v[i] * inv) : 0.0;      // :147-148 + onehot (:157-159, :172-178)
-          da[i] += dv;
-          // B fragment of phase B: rows are the contraction index (row % 4), classes the n index (c % 8)
-          dfrag[(size_t(srow >> 2) * NTL + (c >> 3)) * 32 + (c & 7) * 4 + (srow & 3)] = dv;
-        }
+        const double dv = valid ? ((c == yc ? 1.0 : 0.0) - v[i] * inv) : 0.0;        // :147-148 + onehot (:157-159, :172-178)
+        da[i] += dv;
+        drow[(c >> 3) * 32 + (c & 7) * 4] = dv;
       }
     }
     __syncthreads();  // d complete
@@ -232,19 +267,26 @@ __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(con
     if (want_grad && b_active) {
       // lane (col = lane / 4, row = lane % 4) of the transposed fragment: k-block (col / 4) of the m-tile,
       // word (4 * (rs & 1) + row) * 4 + col % 4 of the row block rs / 2
-      const double* xb = xt + (lane >> 4) * 32 + (lane & 3) * 4 + ((lane >> 2) & 3);
-      for (int rs = rs0; rs < rs1; ++rs) {
-        double b[NTL];
+      // (rs0 and rs1 are even: a row block of 8 rows is two row steps, always taken together)
+      const double* xr = xt + size_t(rs0 >> 1) * kb * 32 + mt0 * 64 + (lane >> 4) * 32 + (lane & 3) * 4 + ((lane >> 2) & 3);
+      const double* df = dfrag + size_t(rs0) * NTL * 32 + lane;
+      const int xstep = kb * 32;
+      for (int rs = rs0; rs < rs1; rs += 2, xr += xstep, df += 2 * NTL * 32) {
+        double b0[NTL], b1[NTL];
 #pragma unroll
-        for (int j = 0; j < NTL; ++j) b[j] = dfrag[(size_t(rs) * NTL + j) * 32 + lane];
-        const double* xr = xb + size_t(rs >> 1) * kb * 32 + (rs & 1) * 16;
+        for (int j = 0; j < NTL; ++j) {
+          b0[j] = df[j * 32];
+          b1[j] = df[(NTL + j) * 32];
+        }
 #pragma unroll
         for (int m = 0; m < MPW; ++m) {
-          const int mt = mt0 + 8 * m;
-          if (mt < MT) {
-            const double a = xr[mt * 64];
+          if (m == 0 || mt0 + 8 * m < MT) {
+            const double a0 = xr[m * 512], a1 = xr[m * 512 + 16];
 #pragma unroll
-            for (int j = 0; j < NTL; ++j) dmma884(g[m][j][0], g[m][j][1], a, b[j]);
+            for (int j = 0; j < NTL; ++j) {
+              dmma884(g[m][j][0], g[m][j][1], a0, b0[j]);
+              dmma884(g[m][j][0], g[m][j][1], a1, b1[j]);
+            }
           }
         }
       }
@@ -273,7 +315,7 @@ __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(con
     }
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) part[tid * 4 + i] = da[i];
+  for (int i = 0; i < 4; ++i) part[tid * 4 + i] = i < CPT ? da[i < CPT ? i : 0] : 0.0;
   __syncthreads();
   double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
   for (int idx = tid; idx < ncls * kpad; idx += NT) {
@@ -289,7 +331,7 @@ __global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(con
     my_scratch[4 + tid] = sum;
   }
   __syncthreads();  // part and rg are consumed
-  part[tid] = lp_acc;
+  part[tid] = lp_acc - log(prod);
   __syncthreads();
   if (tid == 0) {
     double sum = 0.0;
@@ -316,9 +358,9 @@ static size_t mma_smem_bytes(const Tiling& t, int stages, int ntl, size_t* stage
   return size_t(stages) * stage + doubles * sizeof(double) + size_t(stages) * sizeof(uint64_t) + 16;
 }
 
-template <int NTL, int MPW>
+template <int NTL, int MPW, int TPR, int CPT>
 static int launch_mma_inst(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
-  auto kern = glm_categorical_mma_kernel<NTL, MPW>;
+  auto kern = glm_categorical_mma_kernel<NTL, MPW, TPR, CPT>;
   static std::atomic<size_t> configured[64];
   int dev = 0;
   SC_CUDA(cudaGetDevice(&dev));
@@ -335,7 +377,7 @@ static int launch_mma_inst(const GlmKernelParams& p, int grid, size_t smem, cuda
 int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
-  if (t.layout != kLayoutMma || (t.kpad & 7) || (t.R != 32 && t.R != 64))
+  if (t.layout != kLayoutMma || (t.kpad & 7) || t.R != (t.kpad <= 64 ? 64 : 32))
     return fail(STAN_CUDA_ERR_ARG, "launch_glm: categorical_logit DMMA kernel needs the fragment tile layout");
   const int ncls = io.ncls;
   if (ncls < 1 || ncls > kMaxClasses || size_t(ncls) * t.kpad > size_t(kMaxClassWeights))
@@ -376,15 +418,18 @@ int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Work
   p.group_size = group_size;
   p.stage_bytes = uint32_t(stage_bytes);
   p.ncls = ncls;
-  const int mpw = (MT + 7) / 8;  // 1 .. 4
-  if (ntl == 1) {
-    if (mpw <= 1) return launch_mma_inst<1, 1>(p, grid, smem, stream);
-    if (mpw == 2) return launch_mma_inst<1, 2>(p, grid, smem, stream);
-    return launch_mma_inst<1, 4>(p, grid, smem, stream);
+  if (t.R == 64) {  // k_pad <= 64: one m-tile per warp, four threads per row in the softmax phase
+    const int cpt = (ncls + 3) / 4;
+    switch (cpt) {
+      case 1: return launch_mma_inst<1, 1, 4, 1>(p, grid, smem, stream);
+      case 2: return launch_mma_inst<1, 1, 4, 2>(p, grid, smem, stream);
+      case 3: return launch_mma_inst<2, 1, 4, 3>(p, grid, smem, stream);
+      default: return launch_mma_inst<2, 1, 4, 4>(p, grid, smem, stream);
+    }
   }
-  if (mpw <= 1) return launch_mma_inst<2, 1>(p, grid, smem, stream);
-  if (mpw == 2) return launch_mma_inst<2, 2>(p, grid, smem, stream);
-  return launch_mma_inst<2, 4>(p, grid, smem, stream);
+  const bool wide = MT > 16;  // m-tiles per warp: 2 up to k_pad 128, 4 up to 256
+  if (ntl == 1) return wide ? launch_mma_inst<1, 4, 8, 1>(p, grid, smem, stream) : launch_mma_inst<1, 2, 8, 1>(p, grid, smem, stream);
+  return wide ? launch_mma_inst<2, 4, 8, 2>(p, grid, smem, stream) : launch_mma_inst<2, 2, 8, 2>(p, grid, smem, stream);
 }
 
 }  // namespace stancuda

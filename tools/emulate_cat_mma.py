@@ -117,16 +117,20 @@ def emulate(x, y, alpha, beta):
                 rs1 = R // 4 if rpart == RS - 1 else rs0 + per
             if not active:
                 continue
-            xb = (lane >> 4) * 32 + (lane & 3) * 4 + ((lane >> 2) & 3)
-            for rs in range(rs0, rs1):
-                b = [dfrag[(rs * NTL + j) * 32 + lane] for j in range(NTL)]
-                xr = xb + (rs >> 1) * kb * 32 + (rs & 1) * 16
+            # pointer walk of the kernel: two row steps (one row block of 8 rows) per iteration
+            xr = (rs0 >> 1) * kb * 32 + mt0 * 64 + (lane >> 4) * 32 + (lane & 3) * 4 + ((lane >> 2) & 3)
+            df = rs0 * NTL * 32 + lane
+            for rs in range(rs0, rs1, 2):
+                b0 = [dfrag[df + j * 32] for j in range(NTL)]
+                b1 = [dfrag[df + (NTL + j) * 32] for j in range(NTL)]
                 for m in range(MPW):
-                    mt = mt0 + 8 * m
-                    if mt < MT:
-                        a = xt[xr + mt * 64]
+                    if m == 0 or mt0 + 8 * m < MT:
+                        a0, a1 = xt[xr + m * 512], xt[xr + m * 512 + 16]
                         for j in range(NTL):
-                            g[warp, m, j] = dmma(g[warp, m, j], a, b[j])
+                            g[warp, m, j] = dmma(g[warp, m, j], a0, b0[j])
+                            g[warp, m, j] = dmma(g[warp, m, j], a1, b1[j])
+                xr = xr + kb * 32
+                df = df + 2 * NTL * 32
     # CTA reduction
     RSn = 1 if MT >= 8 else 8 // MT
     rg = np.zeros(RSn * kpad * 8 * NTL)
