@@ -190,10 +190,10 @@ STAN_CUDA_API void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm
  * producer warp (csrc/glm_warp.cu), 0 = CTA-synchronous kernel (csrc/glm_fused.cu).  Both compute
  * the same thing from differently tiled copies of X.  Environment: STAN_CUDA_KERNEL=warp|cta. */
 STAN_CUDA_API void stan_cuda_set_kernel(int variant);
-/* categorical_logit kernel for data created afterwards: 0 (default) = vector FP64 kernel on the warp tile
- * layout (csrc/glm_categorical.cu), 1 = FP64 tensor-core kernel (mma.m8n8k4, SASS DMMA) on a tile layout
- * stored in the instruction's fragment order (csrc/glm_categorical_mma.cu; k <= 256, wider x keeps
- * variant 0).  Same results to rounding.  Environment: STAN_CUDA_CATEGORICAL=mma|warp. */
+/* categorical_logit kernel for data created afterwards: 1 (default) = FP64 tensor-core kernel (mma.m8n8k4,
+ * SASS DMMA) on a tile layout stored in the instruction's fragment order (csrc/glm_categorical_mma.cu;
+ * k <= 256, wider x uses variant 0), 0 = vector FP64 kernel on the warp tile layout
+ * (csrc/glm_categorical.cu).  Same results to rounding.  Environment: STAN_CUDA_CATEGORICAL=mma|vector. */
 STAN_CUDA_API void stan_cuda_set_categorical_kernel(int variant);
 
 /* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */

@@ -139,7 +139,7 @@ inline size_t result_cols(const stan_cuda_data* d, const LaunchIO& io) {
 int sm_count(int device);
 
 // tuning knobs (env STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM; 0 = auto)
-struct Tuning { int threads = 0, stages = 0, ctas_per_sm = 0, layout = kLayoutWarp, blocked = 0, cat_mma = 0; };
+struct Tuning { int threads = 0, stages = 0, ctas_per_sm = 0, layout = kLayoutWarp, blocked = 0, cat_mma = 1; };
 const Tuning& tuning();
 
 // relayout kernels (data.cu)

@@ -73,7 +73,7 @@ __device__ __forceinline__ double exp_nonpos(double x) {
 // TPR: threads per row in phase S (4: 64 rows per tile, 8: 32 rows).  CPT: classes per thread in phase S,
 // ceil(classes / TPR).  All four are functions of (k_pad, classes); eight combinations exist (launch below).
 template <int NTL, int MPW, int TPR, int CPT>
-__global__ void __launch_bounds__(kMmaThreads, 2) glm_categorical_mma_kernel(const GlmKernelParams p) {
+__global__ void __launch_bounds__(kMmaThreads, TPR == 4 ? 3 : 2) glm_categorical_mma_kernel(const GlmKernelParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr int NT = kMmaThreads;
   constexpr int ldl = NTL == 1 ? 8 : 24;  // row stride of the partial lin block (== 8 mod 16: conflict-free C-fragment stores)
@@ -388,10 +388,21 @@ int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Work
   const int MT = t.kpad / 8;
   if (MT > 32) return fail(STAN_CUDA_ERR_ARG, "launch_glm: categorical_logit DMMA kernel supports k_pad <= 256");
   const int sms = sm_count(d->device);
-  // two CTAs per SM when two stages fit in half of the shared memory, else one CTA with up to four stages
-  const size_t half = (size_t(228) * 1024) / 2 - 1024 - 64;
-  int ctas_per_sm = mma_smem_bytes(t, 2, ntl, nullptr) <= half ? 2 : 1;
-  const size_t budget = ctas_per_sm == 2 ? half : size_t(227) * 1024;
+  // the kernel is latency-bound (dependent FP64 chains, three phases between barriers): as many CTAs per SM as
+  // hold two stages each, then as many stages as still fit (<= 4).  The 64-row instantiations (k_pad <= 64) are
+  // compiled for 80 registers, i.e. up to 3 CTAs per SM (K=32: 86 vs 95 us); the 32-row ones keep 128 registers
+  // (their 32-64 KiB tiles allow 2 or 1 CTAs anyway, and the register cap cost them 4-9 %)
+  int ctas_per_sm = t.R == 64 ? 3 : 2;
+  size_t budget = 0;
+  for (; ctas_per_sm >= 1; --ctas_per_sm) {
+    budget = ctas_per_sm == 1 ? size_t(227) * 1024 : (size_t(228) * 1024) / ctas_per_sm - 1024 - 64;
+    if (mma_smem_bytes(t, 2, ntl, nullptr) <= budget) break;
+  }
+  if (ctas_per_sm < 1) return fail(STAN_CUDA_ERR_ARG, "launch_glm: categorical_logit tile does not fit shared memory");
+  if (tuning().ctas_per_sm > 0 && tuning().ctas_per_sm < ctas_per_sm) {
+    ctas_per_sm = tuning().ctas_per_sm;
+    budget = ctas_per_sm == 1 ? size_t(227) * 1024 : (size_t(228) * 1024) / ctas_per_sm - 1024 - 64;
+  }
   int stages = 4;
   while (stages > 2 && mma_smem_bytes(t, stages, ntl, nullptr) > budget) --stages;
   size_t stage_bytes = 0;

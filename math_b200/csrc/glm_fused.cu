@@ -236,7 +236,7 @@ static Tuning& tuning_mut() {
     const char* kv = getenv("STAN_CUDA_KERNEL");
     u.layout = (kv && (kv[0] == 'c' || kv[0] == 'C')) ? kLayoutCta : kLayoutWarp;
     const char* cv = getenv("STAN_CUDA_CATEGORICAL");
-    u.cat_mma = (cv && (cv[0] == 'm' || cv[0] == 'M')) ? 1 : 0;
+    u.cat_mma = (cv && (cv[0] == 'w' || cv[0] == 'W' || cv[0] == 'v' || cv[0] == 'V')) ? 0 : 1;
     return u;
   }();
   return t;

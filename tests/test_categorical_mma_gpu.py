@@ -22,7 +22,6 @@ def glm():
     lib().stan_cuda_set_categorical_kernel(1)
     yield g
     g.cache_clear()
-    lib().stan_cuda_set_categorical_kernel(0)
 
 
 @pytest.fixture(scope="module")

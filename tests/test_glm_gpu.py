@@ -13,15 +13,18 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module", params=["warp", "cta"])
 def glm(request):
-    """The whole module runs once per kernel variant (csrc/glm_warp.cu, csrc/glm_fused.cu)."""
+    """The whole module runs once per kernel variant (csrc/glm_warp.cu, csrc/glm_fused.cu); the categorical_logit
+    cases run on the DMMA kernel in the first pass (the default) and on the vector kernel in the second."""
     from math_b200 import glm as g
     from math_b200._lib import lib
     g.init(1)
     g.cache_clear()
     lib().stan_cuda_set_kernel(1 if request.param == "warp" else 0)
+    lib().stan_cuda_set_categorical_kernel(1 if request.param == "warp" else 0)
     yield g
     g.cache_clear()
     lib().stan_cuda_set_kernel(1)
+    lib().stan_cuda_set_categorical_kernel(1)
 
 
 @pytest.fixture(scope="module")

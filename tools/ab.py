@@ -24,7 +24,7 @@ def main():
     ap.add_argument("--ctas", type=int, default=0)
     ap.add_argument("--shapes", default="")
     ap.add_argument("--widened", action="store_true", help="neg_binomial_2_log and ordered_logistic shapes instead")
-    ap.add_argument("--cat-kernel", default="warp", help="categorical_logit kernel: warp (vector FP64) | mma (DMMA)")
+    ap.add_argument("--cat-kernel", default="mma", help="categorical_logit kernel: warp (vector FP64) | mma (DMMA)")
     ap.add_argument("--only", default="", help="--widened: only the families whose name contains this")
     args = ap.parse_args()
     import torch
@@ -80,6 +80,7 @@ def widened(args, torch, glm, peak, stream):
              ("categorical_logit", 1_000_000, 32, 16)]
     from math_b200._lib import lib
     lib().stan_cuda_set_categorical_kernel(1 if args.cat_kernel == "mma" else 0)
+    lib().stan_cuda_set_tuning(0, args.stages, args.ctas)
     if args.cat_kernel == "mma":
         cases += [("categorical_logit", 1_250_000, 128, 16), ("categorical_logit", 1_000_000, 64, 8),
                   ("categorical_logit", 500_000, 256, 16)]
