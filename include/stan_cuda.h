@@ -19,6 +19,9 @@
  *                                  ordered_logistic_glm_lpmf   stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:93-199
  *                                  categorical_logit_glm_lpmf  stan/math/prim/mat/prob/categorical_logit_glm_lpmf.hpp:74-190
  *   stan_cuda_normal_lpdf_eval   the loop of normal_lpdf      stan/math/prim/scal/prob/normal_lpdf.hpp:67-110
+ *   stan_cuda_density_eval       the loops of the vectorised elementwise densities
+ *                                  bernoulli_logit_lpmf      stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
+ *                                  poisson_log_lpmf          stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93
  *   stan_cuda_data_* / cache_*   matrix_cl + to_matrix_cl      stan/math/opencl/matrix_cl.hpp:32-454, stan/math/opencl/copy.hpp:37-93
  *                                and the cache-by-call_id of the MPI backend
  *                                  stan/math/prim/mat/functor/mpi_parallel_call.hpp:40-89
@@ -45,6 +48,9 @@
  *                             (y NaN, mu not finite, sigma not > 0: normal_lpdf.hpp:51-53).  The kernel
  *                             tests every element on its way through, so the wrapper runs no O(N) check
  *                             loops; on this code it runs the reference's checks, which throw
+ *    4  STAN_CUDA_LOG_ZERO    (poisson_log_lpmf) some log rate is +inf, or -inf next to a non-zero count: the
+ *                             reference returns LOG_ZERO before building any partial (poisson_log_lpmf.hpp:51-62);
+ *                             *lp is -inf, no partial was written; the C++ wrapper returns LOG_ZERO
  *   <0  failure (bad argument, CUDA or NCCL error); stan_cuda_last_error() has the text;
  *       the C++ wrapper throws std::system_error (cf. stan/math/opencl/err/check_opencl.hpp)
  *
@@ -72,6 +78,7 @@ extern "C" {
 #define STAN_CUDA_NONFINITE 1
 #define STAN_CUDA_BAD_OUTCOME 2
 #define STAN_CUDA_BAD_OPERAND 3
+#define STAN_CUDA_LOG_ZERO 4
 #define STAN_CUDA_ERR_ARG (-1)
 #define STAN_CUDA_ERR_CUDA (-2)
 #define STAN_CUDA_ERR_NCCL (-3)
@@ -155,6 +162,24 @@ typedef struct stan_cuda_normal_args {
   double* dy;          /* [y_len] */
 } stan_cuda_normal_args;
 
+/* Vectorised elementwise densities with an integer outcome and one real operand: value + partials of the
+ * operand in one pass (the pattern of stan_cuda_normal_lpdf_eval for the lpmf's whose
+ * per-element terms are the epilogues of the GLM kernels). */
+#define STAN_CUDA_DENSITY_BERNOULLI_LOGIT 1 /* bernoulli_logit_lpmf(n | theta)  prim/scal/prob/bernoulli_logit_lpmf.hpp:28-89 */
+#define STAN_CUDA_DENSITY_POISSON_LOG 2     /* poisson_log_lpmf(n | alpha)      prim/scal/prob/poisson_log_lpmf.hpp:22-97 */
+
+typedef struct stan_cuda_density_args {
+  int32_t density;      /* STAN_CUDA_DENSITY_* */
+  uint32_t flags;       /* STAN_CUDA_LP_CONST (poisson: -sum lgamma(n+1)) | LP_MAIN | NEED_DALPHA (= d/dtheta) */
+  int64_t n;            /* max_size(y, theta) */
+  const int32_t* y;     /* host; integer outcomes: immutable data, cached on the device when y_len == n */
+  int64_t y_len;        /* 1 or n */
+  const double* theta;  /* host; logit (bernoulli_logit) or log rate (poisson_log) */
+  int64_t theta_len;    /* 1 or n */
+  double* lp;           /* [1] */
+  double* dtheta;       /* [theta_len]: per element, or the sum over n for a scalar operand */
+} stan_cuda_density_args;
+
 typedef struct stan_cuda_stats_t {
   uint64_t cache_hits;
   uint64_t cache_misses;
@@ -199,6 +224,11 @@ STAN_CUDA_API void stan_cuda_set_categorical_kernel(int variant);
 /* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */
 STAN_CUDA_API int stan_cuda_glm_eval(const stan_cuda_glm_args* a);
 STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
+/* Returns STAN_CUDA_BAD_OPERAND when an outcome is outside the density's support (bernoulli_logit: not in
+ * {0, 1}, bernoulli_logit_lpmf.hpp:42; poisson_log: negative, poisson_log_lpmf.hpp:38) or the operand is NaN
+ * (:43 / :39) -- every element is tested inside the kernel, the wrapper then runs the reference's own checks
+ * to throw the identical exception -- and STAN_CUDA_LOG_ZERO as described above. */
+STAN_CUDA_API int stan_cuda_density_eval(const stan_cuda_density_args* a);
 /* Page-locked staging memory of the calling thread (at least `bytes`, valid until the thread's next
  * call with a larger size).  Operands gathered into it upload by DMA without a bounce buffer. */
 STAN_CUDA_API void* stan_cuda_host_staging(size_t bytes);

@@ -6,7 +6,7 @@ that identical argument blocks can be handed to the CUDA library and to the CPU 
 """
 import ctypes as C
 
-OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND = 0, 1, 2, 3
+OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND, LOG_ZERO = 0, 1, 2, 3, 4
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
 
 BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID, NEG_BINOMIAL_2_LOG, ORDERED_LOGISTIC = 0, 1, 2, 3, 4
@@ -72,6 +72,24 @@ class NormalArgs(C.Structure):
     ]
 
 
+DENSITY_BERNOULLI_LOGIT, DENSITY_POISSON_LOG = 1, 2
+DENSITIES = {"bernoulli_logit": DENSITY_BERNOULLI_LOGIT, "poisson_log": DENSITY_POISSON_LOG}
+
+
+class DensityArgs(C.Structure):
+    _fields_ = [
+        ("density", C.c_int32),
+        ("flags", C.c_uint32),
+        ("n", C.c_int64),
+        ("y", C.c_void_p),
+        ("y_len", C.c_int64),
+        ("theta", C.c_void_p),
+        ("theta_len", C.c_int64),
+        ("lp", C.c_void_p),
+        ("dtheta", C.c_void_p),
+    ]
+
+
 class Stats(C.Structure):
     _fields_ = [
         ("cache_hits", C.c_uint64),
@@ -99,6 +117,7 @@ PROTOTYPES = {
     "stan_cuda_set_kernel": (None, [C.c_int]),
     "stan_cuda_set_categorical_kernel": (None, [C.c_int]),
     "stan_cuda_glm_eval": (C.c_int, [C.POINTER(GlmArgs)]),
+    "stan_cuda_density_eval": (C.c_int, [C.POINTER(DensityArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
     "stan_cuda_host_staging": (C.c_void_p, [C.c_size_t]),
     "stan_cuda_cache_invalidate": (C.c_int, [C.c_void_p]),

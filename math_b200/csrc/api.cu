@@ -530,6 +530,107 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+// =============================================================================================
+// vectorised elementwise densities (density.cu)
+// =============================================================================================
+static uint64_t fingerprint_ivec(const int32_t* v, int64_t n) {
+  uint64_t h = 1469598103934665603ull;
+  const int64_t step = n > 128 ? n / 128 : 1;
+  for (int64_t i = 0; i < n; i += step) h = fnv(h, uint64_t(uint32_t(v[i])));
+  return h;
+}
+
+// integer outcomes are immutable data: cached on the device like the y of a GLM (key kind 3)
+static int get_ivec_entry(const int32_t* v, int64_t n, int device, cudaStream_t stream, std::shared_ptr<Entry>* out) {
+  Key key(3, uintptr_t(v), 0, n, 0, 0, device);
+  const uint64_t fp = fingerprint_ivec(v, n);
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  auto it = g_cache.find(key);
+  if (it != g_cache.end() && it->second->fingerprint == fp) {
+    counters().cache_hits.fetch_add(1, std::memory_order_relaxed);
+    *out = it->second;
+    return STAN_CUDA_OK;
+  }
+  counters().cache_misses.fetch_add(1, std::memory_order_relaxed);
+  if (it != g_cache.end()) g_cache.erase(it);
+  std::shared_ptr<Entry> e = std::make_shared<Entry>();
+  e->fingerprint = fp;
+  e->vec_device = device;
+  const size_t bytes = ((size_t(n) + 1) & ~size_t(1)) * sizeof(int32_t);
+  SC_CUDA(cudaSetDevice(device));
+  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->vec), bytes));
+  e->bytes = bytes;
+  SC_CUDA(cudaMemcpyAsync(e->vec, v, size_t(n) * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+  SC_CUDA(cudaStreamSynchronize(stream));
+  counters().bytes_uploaded.fetch_add(uint64_t(n) * sizeof(int32_t));
+  g_cache[key] = e;
+  *out = e;
+  return STAN_CUDA_OK;
+}
+
+int density_eval(const stan_cuda_density_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: null args");
+  if (a->density != STAN_CUDA_DENSITY_BERNOULLI_LOGIT && a->density != STAN_CUDA_DENSITY_POISSON_LOG)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: unknown density");
+  if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: negative n");
+  if (a->n == 0) {  // size_zero(n, theta) -> 0 (bernoulli_logit_lpmf.hpp:36-38, poisson_log_lpmf.hpp:32-34)
+    if (a->lp) *a->lp = 0.0;
+    return STAN_CUDA_OK;
+  }
+  if (!a->y || !a->theta) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: null operand");
+  if ((a->y_len != 1 && a->y_len != a->n) || (a->theta_len != 1 && a->theta_len != a->n))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: operand length must be 1 or n");
+  SC_TRY(ensure_init());
+  Context& c = context();
+  const int dev = tl_scope.active ? c.devices[size_t(tl_scope.device) % c.devices.size()] : c.devices[0];
+  ThreadDev* td;
+  SC_TRY(thread_dev(dev, &td));
+  SC_CUDA(cudaSetDevice(dev));
+  const int64_t n = a->n;
+  const bool yv = a->y_len != 1, tv = a->theta_len != 1;
+  const bool need_d = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dtheta;
+  std::shared_ptr<Entry> ycache;
+  if (yv) SC_TRY(get_ivec_entry(a->y, n, dev, td->stream, &ycache));
+  const size_t nal = (size_t(n) + 1) & ~size_t(1);
+  size_t need = 8;
+  if (tv) need += nal;
+  if (need_d && tv) need += nal;
+  SC_TRY(td->reserve_dev(need));
+  SC_TRY(td->reserve_host(8));
+  double* p = td->d_buf;
+  DensityIO io{};
+  io.density = a->density;
+  io.flags = a->flags;
+  io.n = n;
+  io.result = p; p += 8;
+  io.y_vec = yv; io.theta_vec = tv;
+  io.y0 = a->y[0]; io.theta0 = a->theta[0];
+  if (yv) io.y = reinterpret_cast<const int*>(ycache->vec);
+  if (tv) {
+    SC_CUDA(cudaMemcpyAsync(p, a->theta, size_t(n) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    io.theta = p; p += nal;
+  }
+  if (need_d && tv) { io.dtheta_row = p; p += nal; }
+  SC_TRY(launch_density(io, &td->ws, dev, td->stream));
+  SC_CUDA(cudaMemcpyAsync(td->h_pinned, io.result, 5 * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  // the per-element partials travel in the same batch (one synchronisation); on the two codes below the caller
+  // discards them, as the reference has not built any partial at that point either
+  if (io.dtheta_row)
+    SC_CUDA(cudaMemcpyAsync(a->dtheta, io.dtheta_row, size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  SC_CUDA(cudaStreamSynchronize(td->stream));
+  const double* res = td->h_pinned;
+  const unsigned bits = unsigned(res[4]);
+  counters().evals.fetch_add(1, std::memory_order_relaxed);
+  if (bits & 3u) return STAN_CUDA_BAD_OPERAND;
+  if (bits & 4u) {
+    if (a->lp) *a->lp = -INFINITY;
+    return STAN_CUDA_LOG_ZERO;
+  }
+  if (a->lp) *a->lp = res[0];
+  if (need_d && !tv) a->dtheta[0] = res[1];
+  return STAN_CUDA_OK;
+}
+
 // Pinned (page-locked, portable) staging memory of the calling thread: wrappers gather the values of
 // var operands straight into it, so the upload is a full-speed DMA without a bounce buffer.
 void* host_staging(size_t bytes) {
@@ -562,6 +663,7 @@ extern "C" {
 
 int stan_cuda_glm_eval(const stan_cuda_glm_args* a) { return glm_eval(a); }
 int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) { return normal_lpdf_eval(a); }
+int stan_cuda_density_eval(const stan_cuda_density_args* a) { return density_eval(a); }
 void* stan_cuda_host_staging(size_t bytes) { return host_staging(bytes); }
 
 int stan_cuda_cache_invalidate(const void* host_ptr) {

@@ -159,6 +159,18 @@ struct NormalIO {
 };
 int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream_t stream);
 
+// vectorised elementwise densities (density.cu)
+struct DensityIO {
+  int density;
+  uint32_t flags;
+  int64_t n;
+  const int* y; int y_vec; int y0;
+  const double* theta; int theta_vec; double theta0;
+  double* dtheta_row;         // per-element partials (vector operand) or null
+  double* result;             // [5]: lp, sum dtheta, 0, witness, bits (1: outcome outside the support, 2: operand NaN, 4: LOG_ZERO)
+};
+int launch_density(const DensityIO& io, Workspace* ws, int device, cudaStream_t stream);
+
 // counters
 struct Counters {
   std::atomic<uint64_t> cache_hits{0}, cache_misses{0}, bytes_uploaded{0}, evals{0}, launches{0},

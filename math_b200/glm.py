@@ -6,6 +6,8 @@ Same names, argument order and error behaviour as the reference functions
   normal_id_glm_lpdf(y, x, alpha, beta, sigma)    stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp:49-53
   neg_binomial_2_log_glm_lpmf(y, x, alpha, beta, phi)  stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:60-63
   normal_lpdf(y, mu, sigma)                       stan/math/prim/scal/prob/normal_lpdf.hpp:36-39
+  bernoulli_logit_lpmf(n, theta)                  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:28-29
+  poisson_log_lpmf(n, alpha)                      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:22-23
 Each returns (lp, grads) where grads holds what reverse mode would leave in the adjoints of the
 var arguments (alpha, beta, sigma, mu; y on request).  Size mismatches raise ValueError
 (std::invalid_argument), domain violations raise DomainError (std::domain_error).
@@ -417,6 +419,66 @@ def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
     if need_dy:
         grads["y"] = dy
     return float(lp[0]), grads
+
+
+def density_eval(density, n, theta, flags):
+    """Raw C-ABI call stan_cuda_density_eval; dict with rc, lp, dtheta (theta's shape)."""
+    d = _abi.DENSITIES[density] if isinstance(density, str) else density
+    n = np.ascontiguousarray(np.atleast_1d(np.asarray(n, dtype=np.int32)))
+    theta = _f64(theta)
+    size = max(n.size, theta.size) if min(n.size, theta.size) > 0 else 0
+    lp, dth = np.zeros(1), np.zeros(max(theta.size, 1))
+    a = _abi.DensityArgs()
+    a.density, a.flags, a.n = d, flags, size
+    a.y, a.y_len, a.theta, a.theta_len = n.ctypes.data, n.size, theta.ctypes.data, theta.size
+    a.lp, a.dtheta = lp.ctypes.data, dth.ctypes.data
+    rc = check(lib().stan_cuda_density_eval(C.byref(a)))
+    return {"rc": rc, "lp": float(lp[0]), "dtheta": dth[:theta.size].copy()}
+
+
+def _density(function, density, n, theta, propto, theta_var, n_check, n_error, theta_name):
+    """Call sequence of the reference (bernoulli_logit_lpmf.hpp:36-49, poisson_log_lpmf.hpp:32-49): size_zero -> 0,
+    domain errors before the size error, nothing to compute under propto with a constant operand -> 0."""
+    nn = np.atleast_1d(np.asarray(n))
+    th = _f64(theta)
+    if nn.size == 0 or th.size == 0:
+        return 0.0, {"theta": np.zeros(th.size)}
+    size = max(nn.size, th.size)
+    sizes_ok = nn.size in (1, size) and th.size in (1, size)
+    if not sizes_ok or (propto and not theta_var):
+        # no device work: the reference's eager checks, in its order
+        if not n_check(nn):
+            raise n_error
+        if np.any(np.isnan(th)):
+            raise DomainError("%s: %s is nan, but must not be nan!" % (function, theta_name))
+        if not sizes_ok:
+            raise ValueError("%s: Random variable has dimension = %d, expecting dimension = %d" % (function, nn.size, size))
+        return 0.0, {"theta": np.zeros(th.size)}
+    flags = (_abi.LP_MAIN | _abi.NEED_DALPHA) if theta_var else _abi.LP_MAIN
+    if not propto:
+        flags |= _abi.LP_CONST
+    r = density_eval(density, nn, th, flags)
+    if r["rc"] == _abi.BAD_OPERAND:  # the kernel saw a bad element: the reference's checks name it
+        if not n_check(nn):
+            raise n_error
+        raise DomainError("%s: %s is nan, but must not be nan!" % (function, theta_name))
+    if r["rc"] == _abi.LOG_ZERO:     # poisson_log_lpmf.hpp:51-62: LOG_ZERO, no partials
+        return -np.inf, {"theta": np.zeros(th.size)}
+    return r["lp"], {"theta": r["dtheta"]}
+
+
+def bernoulli_logit_lpmf(n, theta, propto=False, theta_var=True):
+    """stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:28-29; grads: theta."""
+    f = "bernoulli_logit_lpmf"
+    return _density(f, "bernoulli_logit", n, theta, propto, theta_var, lambda v: bool(np.all((v >= 0) & (v <= 1))),
+                    DomainError("%s: n must be in the interval [0, 1]" % f), "Logit transformed probability parameter")
+
+
+def poisson_log_lpmf(n, alpha, propto=False, alpha_var=True):
+    """stan/math/prim/scal/prob/poisson_log_lpmf.hpp:22-23; grads: theta (the log rate alpha)."""
+    f = "poisson_log_lpmf"
+    return _density(f, "poisson_log", n, alpha, propto, alpha_var, lambda v: bool(np.all(v >= 0)),
+                    DomainError("%s: Random variable must be >= 0!" % f), "Log rate parameter")
 
 
 class GlmData:

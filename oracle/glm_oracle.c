@@ -352,3 +352,63 @@ int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a) {
   if (a->lp) *a->lp = logp;
   return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
+
+/* Vectorised elementwise densities with an integer outcome.
+ *   bernoulli_logit_lpmf  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
+ *   poisson_log_lpmf      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93
+ * Return codes as the product's: BAD_OPERAND where the reference's eager checks throw (:42-43 / :38-39),
+ * LOG_ZERO where poisson_log_lpmf returns LOG_ZERO before building partials (:51-62). */
+int oracle_density_eval(const stan_cuda_density_args* a) {
+  if (!a || a->n < 0) return STAN_CUDA_ERR_ARG;
+  const int ym = a->y_len != 1, tm = a->theta_len != 1;
+  const int need_d = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dtheta;
+  const int bern = a->density == STAN_CUDA_DENSITY_BERNOULLI_LOGIT;
+  if (!bern && a->density != STAN_CUDA_DENSITY_POISSON_LOG) return STAN_CUDA_ERR_ARG;
+  if (a->n == 0) {
+    if (a->lp) *a->lp = 0.0;
+    return STAN_CUDA_OK;
+  }
+  for (int64_t i = 0; i < a->y_len; ++i)
+    if (a->y[i] < 0 || (bern && a->y[i] > 1)) return STAN_CUDA_BAD_OPERAND;
+  for (int64_t i = 0; i < a->theta_len; ++i)
+    if (isnan(a->theta[i])) return STAN_CUDA_BAD_OPERAND;
+  if (!bern) {
+    for (int64_t i = 0; i < a->n; ++i) {
+      const double al = a->theta[tm ? i : 0];
+      if (al == INFINITY || (al == -INFINITY && a->y[ym ? i : 0] != 0)) {            /* :51-62 */
+        if (a->lp) *a->lp = -INFINITY;
+        return STAN_CUDA_LOG_ZERO;
+      }
+    }
+  }
+  double logp = 0.0;
+  if (need_d) for (int64_t i = 0; i < a->theta_len; ++i) a->dtheta[i] = 0.0;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const int y = a->y[ym ? i : 0];
+    const double th = a->theta[tm ? i : 0];
+    double d;
+    if (bern) {
+      const int sign = 2 * y - 1;                                                  /* :58 */
+      const double ntheta = sign * th;
+      const double e = exp(-ntheta);                                               /* :60 */
+      if (a->flags & STAN_CUDA_LP_MAIN) {
+        if (ntheta > 20.0) logp -= e;                                              /* :63-69 */
+        else if (ntheta < -20.0) logp += ntheta;
+        else logp -= log1p(e);
+      }
+      if (ntheta > 20.0) d = -e;                                                   /* :72-79 */
+      else if (ntheta < -20.0) d = sign;
+      else d = sign * e / (e + 1);
+    } else {
+      const double e = exp(th);                                                    /* :70-74 */
+      if (!(th == -INFINITY && y == 0)) {                                          /* :77-86 */
+        if (a->flags & STAN_CUDA_LP_CONST) logp -= lgamma(y + 1.0);
+        if (a->flags & STAN_CUDA_LP_MAIN) logp += y * th - e;
+      }
+      d = y - e;                                                                   /* :88-90 */
+    }
+    if (need_d) a->dtheta[tm ? i : 0] += d;
+  }
+  if (a->lp) *a->lp = logp;
+  return STAN_CUDA_OK;
+}

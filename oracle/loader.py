@@ -39,6 +39,8 @@ def oracle_lib():
         lib.oracle_glm_eval.argtypes = [C.POINTER(_abi.GlmArgs)]
         lib.oracle_normal_lpdf_eval.restype = C.c_int
         lib.oracle_normal_lpdf_eval.argtypes = [C.POINTER(_abi.NormalArgs)]
+        lib.oracle_density_eval.restype = C.c_int
+        lib.oracle_density_eval.argtypes = [C.POINTER(_abi.DensityArgs)]
         _oracle = lib
     return _oracle
 
@@ -68,6 +70,9 @@ def ref_lib():
                                             C.c_char_p, i]
         lib.stanref_normal_lpdf_value.restype = i
         lib.stanref_normal_lpdf_value.argtypes = [i, l, dp, dp, l, dp, l, dp, C.c_char_p, i]
+        if hasattr(lib, "stanref_density"):
+            lib.stanref_density.restype = i
+            lib.stanref_density.argtypes = [i, i, l, vp, l, dp, l, i, dp, dp, dp, C.c_char_p, i]
         lib.stanref_init_threads.restype = i
         lib.stanref_init_threads.argtypes = [i]
         lib.stanref_shards_create.restype = C.c_void_p
@@ -393,3 +398,48 @@ class RefShards:
             self.close()
         except Exception:
             pass
+
+
+# ------------------------------------------------------------------------------------------
+# vectorised elementwise densities (bernoulli_logit_lpmf, poisson_log_lpmf)
+def density_flags(propto=False, theta_var=True):
+    """include_summand<propto> keeps the data-only term (poisson: -sum lgamma(n + 1)); the parameter term
+    stays whenever theta is a var (include_summand<propto, T>)."""
+    f = (_abi.LP_MAIN | _abi.NEED_DALPHA) if theta_var else (0 if propto else _abi.LP_MAIN)
+    return f | (0 if propto else _abi.LP_CONST)
+
+
+def density_args(density, y, theta, flags):
+    d = _abi.DENSITIES[density] if isinstance(density, str) else density
+    y = np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+    theta = _f64(theta)
+    n = max(y.size, theta.size) if min(y.size, theta.size) > 0 else 0
+    out = {"lp": np.zeros(1), "dtheta": np.zeros(max(theta.size, 1)), "_keep": (y, theta)}
+    a = _abi.DensityArgs()
+    a.density, a.flags, a.n = d, flags, n
+    a.y, a.y_len, a.theta, a.theta_len = y.ctypes.data, y.size, theta.ctypes.data, theta.size
+    a.lp, a.dtheta = out["lp"].ctypes.data, out["dtheta"].ctypes.data
+    return a, out, (y, theta)
+
+
+def oracle_density(density, y, theta, propto=False, flags=None):
+    if flags is None:
+        flags = density_flags(propto)
+    a, out, (y, theta) = density_args(density, y, theta, flags)
+    rc = oracle_lib().oracle_density_eval(C.byref(a))
+    return {"rc": rc, "lp": float(out["lp"][0]), "dtheta": out["dtheta"][:theta.size].copy()}
+
+
+def ref_density(density, y, theta, propto=False, theta_var=True):
+    """The compiled reference; raises RefError where it throws."""
+    d = _abi.DENSITIES[density] if isinstance(density, str) else density
+    y = np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+    theta = _f64(theta)
+    n = max(y.size, theta.size)
+    lp, dth, secs = np.zeros(1), np.zeros(theta.size), np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_density(d, int(propto), n, y.ctypes.data, y.size, theta.ctypes.data, theta.size,
+                                   int(theta_var), lp.ctypes.data, dth.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return {"lp": float(lp[0]), "dtheta": dth, "seconds": float(secs[0])}

@@ -296,6 +296,48 @@ int stanref_normal_lpdf(int propto, long n, const double* y, const double* mu,
       err, errlen);
 }
 
+// Vectorised bernoulli_logit_lpmf (density 1) / poisson_log_lpmf (density 2): n int data (n_len 1 or n),
+// theta a var vector (theta_len n) or var scalar; theta_is_var == 0 evaluates the all-double form (value only).
+int stanref_density(int density, int propto, long n, const int* y, long y_len, const double* theta,
+                    long theta_len, int theta_is_var, double* lp, double* dtheta, double* seconds,
+                    char* err, int errlen) {
+  return guarded(
+      [&]() {
+        std::vector<int> yv(y, y + y_len);
+        const bool ym = y_len != 1, tm = theta_len != 1;
+        auto t0 = std::chrono::steady_clock::now();
+        if (!theta_is_var) {
+          vector_d th = Eigen::Map<const vector_d>(theta, theta_len);
+          double r;
+#define STANREF_DCALL(F, P) (ym ? (tm ? F<P>(yv, th) : F<P>(yv, th[0])) : (tm ? F<P>(yv[0], th) : F<P>(yv[0], th[0])))
+          if (density == 1)
+            r = propto ? STANREF_DCALL(stan::math::bernoulli_logit_lpmf, true) : STANREF_DCALL(stan::math::bernoulli_logit_lpmf, false);
+          else
+            r = propto ? STANREF_DCALL(stan::math::poisson_log_lpmf, true) : STANREF_DCALL(stan::math::poisson_log_lpmf, false);
+          if (lp) *lp = r;
+          return;
+        }
+        vector_v th = make_vars(theta, theta_len);
+        var t0v = th[0];
+        var res;
+#define STANREF_DVCALL(F, P) (ym ? (tm ? F<P>(yv, th) : F<P>(yv, t0v)) : (tm ? F<P>(yv[0], th) : F<P>(yv[0], t0v)))
+        if (density == 1)
+          res = propto ? STANREF_DVCALL(stan::math::bernoulli_logit_lpmf, true) : STANREF_DVCALL(stan::math::bernoulli_logit_lpmf, false);
+        else
+          res = propto ? STANREF_DVCALL(stan::math::poisson_log_lpmf, true) : STANREF_DVCALL(stan::math::poisson_log_lpmf, false);
+#undef STANREF_DCALL
+#undef STANREF_DVCALL
+        res.grad();
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        if (lp) *lp = res.val();
+        if (dtheta) {
+          if (tm) read_adj(th, dtheta); else dtheta[0] = t0v.adj();
+        }
+      },
+      err, errlen);
+}
+
 // All-double normal_lpdf (value only; the reference's known-answer tests use this form,
 // test/prob/normal/normal_test.hpp:11-40).
 int stanref_normal_lpdf_value(int propto, long n, const double* y, const double* mu,

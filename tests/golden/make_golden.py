@@ -191,7 +191,54 @@ for n, k, c, tag in ((153, 71, 4, "big"), (400, 128, 10, "wide"), (1000, 1, 3, "
     beta = rng4.standard_normal((k, c)) * (1.5 / np.sqrt(k))
     add_cat("rand_" + tag, x, rng4.integers(1, c + 1, n), rng4.standard_normal(c), beta)
 
+# vectorised elementwise densities (own key space "dens/", own generator: earlier draws unchanged):
+# the reference's known-answer pairs (test/prob/bernoulli/bernoulli_logit_test.hpp:11-48,
+# test/prob/poisson/poisson_log_test.hpp:11-31) with their literal expected values, the cutoff branches of
+# bernoulli_logit_lpmf (|theta| > 20), vector / scalar operands, propto on and off
+dens_names = []
+
+
+def add_dens(name, density, y, theta, propto=False, value_only=None):
+    r = L.ref_density(density, y, theta, propto=propto)
+    p = "dens/%s/" % name
+    out[p + "density"] = np.array(L._abi.DENSITIES[density])
+    out[p + "y"] = np.atleast_1d(np.asarray(y, np.int32))
+    out[p + "theta"] = np.atleast_1d(np.asarray(theta, float))
+    out[p + "propto"] = np.array(int(propto))
+    out[p + "lp"], out[p + "dtheta"] = np.array(r["lp"]), r["dtheta"]
+    if value_only is not None:
+        out[p + "known_answer"] = np.array(value_only)
+    dens_names.append(name)
+
+
+def _logit(q):
+    return float(np.log(q / (1.0 - q)))
+
+
+for i, (yy, th, ka) in enumerate([(1, _logit(0.25), np.log(0.25)), (0, _logit(0.25), np.log(0.75)),
+                                  (1, _logit(0.01), np.log(0.01)), (0, _logit(0.01), np.log(0.99)), (0, 25.0, -25.0),
+                                  (1, -25.0, -25.0), (0, -25.0, -np.exp(-25.0))]):
+    add_dens("bern_ka%d" % i, "bernoulli_logit", [yy], [th], value_only=ka)
+for i, (yy, al, ka) in enumerate([(17, np.log(13.0), -2.900934373290765311282), (192, np.log(42.0), -145.3546649655311853166),
+                                  (0, np.log(3.0), -3.0)]):
+    add_dens("pois_ka%d" % i, "poisson_log", [yy], [al], value_only=ka)
+rng5 = np.random.default_rng(20191108)
+th5 = np.concatenate([rng5.standard_normal(2000) * 3, [25.0, -25.0, 21.0, -21.0, 19.99, -19.99, 700.0, -700.0]])
+y5 = (rng5.random(th5.size) < 0.5).astype(np.int32)
+c5 = rng5.poisson(3.0, th5.size).astype(np.int32)
+al5 = np.concatenate([rng5.standard_normal(2000) * 1.5, [5.0, -5.0, 20.0, -30.0, 0.0, 1e-3, -745.0, 6.5]])
+for propto in (False, True):
+    s = "_propto" if propto else ""
+    add_dens("bern_vec" + s, "bernoulli_logit", y5, th5, propto=propto)
+    add_dens("pois_vec" + s, "poisson_log", c5, al5, propto=propto)
+add_dens("bern_scalar_theta", "bernoulli_logit", y5, [0.3])
+add_dens("bern_scalar_n", "bernoulli_logit", [1], th5)
+add_dens("pois_scalar_alpha", "poisson_log", c5, [0.7])
+add_dens("pois_scalar_n", "poisson_log", [4], al5)
+add_dens("pois_minus_inf_zero_count", "poisson_log", [0, 2, 0], [-np.inf, 0.1, 0.4])
+
 out["glm_cases"] = np.array(names)
+out["dens_cases"] = np.array(dens_names)
 out["cat_cases"] = np.array(cat_names)
 out["ord_cases"] = np.array(ord_names)
 out["normal_cases"] = np.array(nl)

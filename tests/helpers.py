@@ -126,3 +126,26 @@ def synth_categorical(n, k, n_classes, seed):
     z = x @ beta_true + alpha + rng.gumbel(size=(n, n_classes))
     y = (1 + np.argmax(z, axis=1)).astype(np.int32)
     return {"x": x, "y": y, "alpha": alpha + 0.1, "beta": beta_true + 0.05 * rng.standard_normal((k, n_classes))}
+
+
+def dens_case(golden, name):
+    p = "dens/%s/" % name
+    c = {k: golden[p + k] for k in ("y", "theta", "dtheta")}
+    c["density"], c["propto"], c["lp"] = int(golden[p + "density"]), bool(golden[p + "propto"]), float(golden[p + "lp"])
+    if p + "known_answer" in golden.files:
+        c["known_answer"] = float(golden[p + "known_answer"])
+    return c
+
+
+def check_dens_result(r, c, what, rtol=RTOL):
+    assert_close(r["lp"], c["lp"], what + " lp", rtol)
+    assert_close(r["dtheta"], c["dtheta"], what + " dtheta", rtol)   # the parity metric of SURVEY 8(d)
+    # and element by element (the partials of a vector operand do not share a scale): relative to the element
+    # itself, floored at 1e-6 of the terms it is a difference of (poisson: n - exp(alpha))
+    got, ref = np.asarray(r["dtheta"], float), np.asarray(c["dtheta"], float)
+    if ref.size > 1:
+        theta, y = np.asarray(c["theta"], float), np.asarray(c["y"], float)
+        with np.errstate(over="ignore"):
+            scale = np.abs(y) + np.exp(theta) if c["density"] == _abi.DENSITY_POISSON_LOG else np.ones(ref.size)
+        err = np.abs(got - ref) / np.maximum(np.maximum(np.abs(ref), 1e-6 * np.minimum(scale, 1e300)), 1e-300)
+        assert not (err > rtol).any(), "%s dtheta: %d components off, worst %.3e" % (what, int((err > rtol).sum()), float(err.max()))

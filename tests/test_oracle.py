@@ -4,8 +4,9 @@ import numpy as np
 import pytest
 
 from oracle import loader as L
-from tests.helpers import (assert_close, cat_case, check_cat_result, check_glm_result, check_ord_result, glm_case,
-                           normal_case, ord_case, synth_categorical, synth_glm, synth_ordered)
+from tests.helpers import (assert_close, cat_case, check_cat_result, check_dens_result, check_glm_result,
+                           check_ord_result, dens_case, glm_case, normal_case, ord_case, synth_categorical, synth_glm,
+                           synth_ordered)
 from math_b200 import _abi
 
 
@@ -105,6 +106,54 @@ def test_oracle_categorical_logit_vs_compiled_reference(n, k, c):
     ref = L.ref_categorical_logit_glm(s["x"], s["y"], s["alpha"], s["beta"])
     got = L.oracle_categorical_logit_glm(s["x"], s["y"], s["alpha"], s["beta"])
     check_cat_result(got, ref, "categorical %dx%d C=%d" % (n, k, c), rtol=1e-11)
+
+
+def test_oracle_densities_match_golden_and_known_answers(golden):
+    """bernoulli_logit_lpmf / poisson_log_lpmf: outputs of the compiled reference, and the literal expected values
+    of the reference's own tests (test/prob/bernoulli/bernoulli_logit_test.hpp:11-48, test/prob/poisson/poisson_log_test.hpp:11-31)."""
+    assert len(golden["dens_cases"]) >= 19
+    known = 0
+    for name in golden["dens_cases"]:
+        c = dens_case(golden, str(name))
+        r = L.oracle_density(c["density"], c["y"], c["theta"], propto=c["propto"])
+        assert r["rc"] == 0, name
+        check_dens_result(r, c, "oracle vs golden dens " + str(name), rtol=1e-12)
+        if "known_answer" in c:
+            known += 1
+            assert abs(r["lp"] - c["known_answer"]) <= 1e-13 * max(1.0, abs(c["known_answer"])), name
+    assert known == 10
+
+
+def test_oracle_density_codes():
+    """What the product must report where the reference throws or returns LOG_ZERO."""
+    assert L.oracle_density("bernoulli_logit", [2], [0.1])["rc"] == _abi.BAD_OPERAND
+    assert L.oracle_density("bernoulli_logit", [1, 0], [0.1, np.nan])["rc"] == _abi.BAD_OPERAND
+    assert L.oracle_density("poisson_log", [-1], [0.1])["rc"] == _abi.BAD_OPERAND
+    r = L.oracle_density("poisson_log", [1, 2], [-np.inf, 0.1])
+    assert r["rc"] == _abi.LOG_ZERO and r["lp"] == -np.inf
+    assert L.oracle_density("poisson_log", [0, 2], [np.inf, 0.1])["rc"] == _abi.LOG_ZERO
+    assert L.oracle_density("poisson_log", [0, 2], [-np.inf, 0.1])["rc"] == 0
+    assert L.oracle_density("poisson_log", [], [])["lp"] == 0.0
+
+
+@needs_ref
+@pytest.mark.parametrize("density", ["bernoulli_logit", "poisson_log"])
+def test_oracle_density_vs_compiled_reference(density):
+    rng = np.random.default_rng(3)
+    n = 5000
+    theta = rng.standard_normal(n) * (4.0 if density == "bernoulli_logit" else 1.5)
+    y = (rng.random(n) < 0.4).astype(np.int32) if density == "bernoulli_logit" else rng.poisson(2.0, n).astype(np.int32)
+    for propto in (False, True):
+        for yy, th in ((y, theta), (y, theta[:1]), (y[:1], theta)):
+            ref = L.ref_density(density, yy, th, propto=propto)
+            got = L.oracle_density(density, yy, th, propto=propto)
+            assert got["rc"] == 0
+            assert_close(got["lp"], ref["lp"], "lp", 1e-13)
+            assert_close(got["dtheta"], ref["dtheta"], "dtheta", 1e-13)
+    for bad in (([2] if density == "bernoulli_logit" else [-1], [0.1]), ([1], [np.nan])):
+        with pytest.raises(L.RefError) as e:
+            L.ref_density(density, *bad)
+        assert e.value.rc == 1
 
 
 @needs_ref
