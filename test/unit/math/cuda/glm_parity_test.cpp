@@ -383,6 +383,93 @@ TEST(CudaNormalLpdf, same_exceptions_as_the_reference) {
   stan::math::recover_memory();
 }
 
+// --- vectorised elementwise densities -------------------------------------------
+TEST(CudaIntDensity, bernoulli_logit_and_poisson_log_match_reference_loop) {
+  const int n = 100000;
+  Problem p = make_problem(n, 1, 9);
+  VectorXd th_d = 3.0 * p.y_norm, al_d = 0.5 * p.y_norm;
+  th_d[5] = 25.0;   // the cutoff branches of bernoulli_logit_lpmf.hpp:63-79
+  th_d[6] = -25.0;
+  vector_v theta = to_v(th_d), alpha = to_v(al_d);
+  std::vector<var> theta_sv(theta.data(), theta.data() + n);
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("bernoulli_logit_lpmf", bernoulli_logit_lpmf(p.y_bern, theta),
+                   bernoulli_logit_lpmf_reference_cpu<false>(p.y_bern, theta), adj(theta));
+  STAN_CUDA_PARITY("bernoulli_logit_lpmf propto", bernoulli_logit_lpmf<true>(p.y_bern, theta),
+                   bernoulli_logit_lpmf_reference_cpu<true>(p.y_bern, theta), adj(theta));
+  STAN_CUDA_PARITY("bernoulli_logit_lpmf scalar n", bernoulli_logit_lpmf(1, theta),
+                   bernoulli_logit_lpmf_reference_cpu<false>(1, theta), adj(theta));
+  STAN_CUDA_PARITY("poisson_log_lpmf", poisson_log_lpmf(p.y_pois, alpha),
+                   poisson_log_lpmf_reference_cpu<false>(p.y_pois, alpha), adj(alpha));
+  STAN_CUDA_PARITY("poisson_log_lpmf propto", poisson_log_lpmf<true>(p.y_pois, alpha),
+                   poisson_log_lpmf_reference_cpu<true>(p.y_pois, alpha), adj(alpha));
+  {  // std::vector<var> operand
+    var lp = bernoulli_logit_lpmf(p.y_bern, theta_sv);
+    var lp_ref = bernoulli_logit_lpmf_reference_cpu<false>(p.y_bern, theta);
+    expect_rel(lp.val(), lp_ref.val(), std::fabs(lp_ref.val()), "std::vector<var> theta");
+  }
+  // double operands: value only, double return type
+  std::vector<double> th_sd(th_d.data(), th_d.data() + n);
+  const double v = bernoulli_logit_lpmf(p.y_bern, th_sd);
+  expect_rel(v, bernoulli_logit_lpmf_reference_cpu<false>(p.y_bern, th_sd), std::fabs(v), "double theta");
+  const double w = poisson_log_lpmf(p.y_pois, al_d);
+  expect_rel(w, poisson_log_lpmf_reference_cpu<false>(p.y_pois, al_d), std::fabs(w), "double alpha");
+  EXPECT_EQ(0.0, poisson_log_lpmf<true>(p.y_pois, al_d));  // propto with a constant operand
+  // known answers of test/prob/bernoulli/bernoulli_logit_test.hpp:11-48 and test/prob/poisson/poisson_log_test.hpp:11-31
+  std::vector<int> n1{1}, n17{17};
+  std::vector<double> t1{std::log(0.25 / 0.75)}, a13{std::log(13.0)};
+  EXPECT_NEAR(std::log(0.25), bernoulli_logit_lpmf(n1, t1), 1e-14);
+  EXPECT_NEAR(-2.900934373290765311282, poisson_log_lpmf(n17, a13), 1e-13);
+  stan::math::recover_memory();
+}
+
+TEST(CudaIntDensity, same_exceptions_and_log_zero_as_the_reference) {
+  using namespace stan::math;  // NOLINT
+  const int n = 2000;
+  std::vector<int> y(n, 1), y_bad = y, y_neg = y;
+  y_bad[1500] = 2;
+  y_neg[3] = -1;
+  vector_v theta = to_v(VectorXd::LinSpaced(n, -2, 2));
+  vector_v theta_nan = to_v(VectorXd::LinSpaced(n, -2, 2));
+  theta_nan[1999] = NAN;
+  EXPECT_THROW(bernoulli_logit_lpmf(y_bad, theta), std::domain_error);
+  EXPECT_THROW(bernoulli_logit_lpmf(y, theta_nan), std::domain_error);
+  EXPECT_THROW(poisson_log_lpmf(y_neg, theta), std::domain_error);
+  EXPECT_THROW(poisson_log_lpmf(y, theta_nan), std::domain_error);
+  vector_v theta_short = to_v(VectorXd::LinSpaced(n - 1, -2, 2));
+  EXPECT_THROW(bernoulli_logit_lpmf(y, theta_short), std::invalid_argument);
+  EXPECT_THROW(poisson_log_lpmf(y, theta_short), std::invalid_argument);
+  std::string m_gpu, m_cpu;
+  try {
+    bernoulli_logit_lpmf(y_bad, theta);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    bernoulli_logit_lpmf_reference_cpu<false>(y_bad, theta);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  // LOG_ZERO early returns of poisson_log_lpmf.hpp:51-62
+  vector_v a_inf = to_v(VectorXd::Constant(n, 0.1)), a_minf = to_v(VectorXd::Constant(n, 0.1));
+  a_inf[7] = INFINITY;
+  a_minf[7] = -INFINITY;
+  EXPECT_EQ(LOG_ZERO, poisson_log_lpmf(y, a_inf).val());
+  EXPECT_EQ(LOG_ZERO, poisson_log_lpmf(y, a_minf).val());
+  std::vector<int> y0 = y;
+  y0[7] = 0;  // -inf next to a zero count contributes nothing (:77)
+  var lp = poisson_log_lpmf(y0, a_minf);
+  var lp_ref = poisson_log_lpmf_reference_cpu<false>(y0, a_minf);
+  EXPECT_TRUE(std::isfinite(lp.val()));
+  expect_rel(lp.val(), lp_ref.val(), std::fabs(lp_ref.val()), "-inf with zero count");
+  std::vector<int> none;
+  vector_v empty(0);
+  EXPECT_EQ(0.0, bernoulli_logit_lpmf(none, empty).val());
+  stan::math::recover_memory();
+}
+
 // --- map_rect: shards dispatched to devices ------------------------------------------------------
 struct glm_shard {
   template <typename T1, typename T2>

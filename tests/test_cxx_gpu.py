@@ -3,6 +3,8 @@
 
 * cuda_glm_parity_test: the STAN_CUDA path through the reference's own C++ signatures (var and
   double arguments) against the unmodified reference body, 1e-10.
+* cuda_int_density_distr_test: the reference's distribution-test fixture and its bernoulli_logit / poisson_log test
+  classes (included unmodified) instantiated for the argument kinds routed to the device.
 * ref_*: the reference's OWN unit tests, compiled unmodified with the overlay include path and
   -DSTAN_CUDA -- the drop-in contract."""
 import os
@@ -14,7 +16,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CXX_DIR = os.path.join(ROOT, "build", "cxx")
 BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_poisson_log_glm_lpmf_test",
             "ref_normal_id_glm_lpdf_test", "ref_neg_binomial_2_log_glm_lpmf_test", "ref_ordered_logistic_glm_lpmf_test", "ref_categorical_logit_glm_lpmf_test", "ref_operands_and_partials_test", "ref_precomputed_gradients_test",
-            "ref_map_rect_concurrent_test"]
+            "ref_map_rect_concurrent_test", "cuda_int_density_distr_test", "ref_bernoulli_logit_log_test",
+            "ref_poisson_log_log_test", "ref_bernoulli_logit_test", "ref_poisson_log_test"]
 
 
 @pytest.mark.gpu
