@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -319,6 +319,26 @@ double normal_once(const VectorXd& y, const VectorXd& mu_val, double sigma_val, 
   return t1 - t0;
 }
 
+// vectorised lpmf with an integer outcome and a var vector operand (DENSITY 1: bernoulli_logit_lpmf,
+// 2: poisson_log_lpmf); one evaluation = forward + grad() + reading the N adjoints
+template <bool GPU, int DENSITY>
+double int_density_once(const std::vector<int>& y, const VectorXd& th_val, Result* out) {
+  using namespace stan::math;  // NOLINT
+  start_nested();
+  vector_v th(th_val.size());
+  for (int64_t i = 0; i < th_val.size(); ++i) th[i] = th_val[i];
+  const double t0 = now();
+  var lp = DENSITY == 1 ? (GPU ? bernoulli_logit_lpmf(y, th) : bernoulli_logit_lpmf_reference_cpu<false>(y, th))
+                        : (GPU ? poisson_log_lpmf(y, th) : poisson_log_lpmf_reference_cpu<false>(y, th));
+  grad(lp.vi_);
+  out->lp = lp.val();
+  out->grad.resize(th.size());
+  for (int64_t i = 0; i < th.size(); ++i) out->grad[i] = th[i].adj();
+  const double t1 = now();
+  recover_memory_nested();
+  return t1 - t0;
+}
+
 struct Timing {
   double median = 0, best = 0;
   int reps = 0;
@@ -408,6 +428,35 @@ int run(int argc, char** argv) {
       std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
     }
     std::printf(", \"algorithmic_device_bytes\": %lld}\n", (long long)(3 * n * 8));
+    return 0;
+  }
+
+  if (config == "d1" || config == "d2") {
+    const bool bern = config == "d1";
+    const int64_t n = n_override ? n_override : 1000000;
+    std::vector<int> y(n);
+    VectorXd th(n);
+    Rng r(bern ? 1011 : 1012);
+    for (int64_t i = 0; i < n; ++i) {
+      th[i] = (bern ? 2.0 : 1.0) * r.normal() + (bern ? 0.0 : 0.5);
+      y[i] = bern ? (r.normal() < th[i] ? 1 : 0) : int(std::max(0.0, std::floor(std::exp(th[i]) + r.normal())));
+      th[i] += 0.1 * r.normal();
+    }
+    Result g, c;
+    auto gpu = [&] { return bern ? int_density_once<true, 1>(y, th, &g) : int_density_once<true, 2>(y, th, &g); };
+    auto cpu = [&] { return bern ? int_density_once<false, 1>(y, th, &c) : int_density_once<false, 2>(y, th, &c); };
+    gpu();
+    Timing tg = time_reps(3, reps, 30, gpu);
+    std::printf("\"what\": \"%s N=%lld, n data, operand var vector\", ", bern ? "bernoulli_logit_lpmf" : "poisson_log_lpmf",
+                (long long)n);
+    print_timing("gpu", tg);
+    if (!no_cpu) {
+      Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, cpu);
+      std::printf(", ");
+      print_timing("cpu_reference_1_thread", tc);
+      std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
+    }
+    std::printf(", \"algorithmic_device_bytes\": %lld}\n", (long long)(n * 20));
     return 0;
   }
 

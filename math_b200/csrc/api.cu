@@ -32,6 +32,7 @@ struct Entry {
   int vec_device = -1;
   uint64_t fingerprint = 0;
   size_t bytes = 0;
+  double lgamma_sum = 0.0;     // cached integer outcomes of a density: sum lgamma(v + 1)
   ~Entry() {
     for (Shard& s : shards) free_data_block(s.d);
     if (vec) {
@@ -541,8 +542,9 @@ static uint64_t fingerprint_ivec(const int32_t* v, int64_t n) {
 }
 
 // integer outcomes are immutable data: cached on the device like the y of a GLM (key kind 3)
-static int get_ivec_entry(const int32_t* v, int64_t n, int device, cudaStream_t stream, std::shared_ptr<Entry>* out) {
-  Key key(3, uintptr_t(v), 0, n, 0, 0, device);
+static int get_ivec_entry(const int32_t* v, int64_t n, int device, int want_lgamma, cudaStream_t stream,
+                          std::shared_ptr<Entry>* out) {
+  Key key(3, uintptr_t(v), 0, n, 0, want_lgamma, device);
   const uint64_t fp = fingerprint_ivec(v, n);
   std::lock_guard<std::mutex> lk(g_cache_mu);
   auto it = g_cache.find(key);
@@ -561,7 +563,11 @@ static int get_ivec_entry(const int32_t* v, int64_t n, int device, cudaStream_t 
   SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->vec), bytes));
   e->bytes = bytes;
   SC_CUDA(cudaMemcpyAsync(e->vec, v, size_t(n) * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
-  SC_CUDA(cudaStreamSynchronize(stream));
+  if (want_lgamma) {  // data-only term of poisson_log_lpmf (:79-81), once per data set instead of N lgamma per call
+    SC_TRY(int_vector_stats(reinterpret_cast<const int*>(e->vec), n, 1, stream, &e->lgamma_sum, nullptr, nullptr));
+  } else {
+    SC_CUDA(cudaStreamSynchronize(stream));
+  }
   counters().bytes_uploaded.fetch_add(uint64_t(n) * sizeof(int32_t));
   g_cache[key] = e;
   *out = e;
@@ -590,7 +596,8 @@ int density_eval(const stan_cuda_density_args* a) {
   const bool yv = a->y_len != 1, tv = a->theta_len != 1;
   const bool need_d = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dtheta;
   std::shared_ptr<Entry> ycache;
-  if (yv) SC_TRY(get_ivec_entry(a->y, n, dev, td->stream, &ycache));
+  const bool poisson = a->density == STAN_CUDA_DENSITY_POISSON_LOG;
+  if (yv) SC_TRY(get_ivec_entry(a->y, n, dev, poisson ? 1 : 0, td->stream, &ycache));
   const size_t nal = (size_t(n) + 1) & ~size_t(1);
   size_t need = 8;
   if (tv) need += nal;
@@ -606,6 +613,10 @@ int density_eval(const stan_cuda_density_args* a) {
   io.y_vec = yv; io.theta_vec = tv;
   io.y0 = a->y[0]; io.theta0 = a->theta[0];
   if (yv) io.y = reinterpret_cast<const int*>(ycache->vec);
+  if (poisson) {
+    io.lgamma_cached = 1;
+    io.lgamma_total = yv ? ycache->lgamma_sum : (a->y[0] >= 0 ? double(n) * lgamma(double(a->y[0]) + 1.0) : 0.0);
+  }
   if (tv) {
     SC_CUDA(cudaMemcpyAsync(p, a->theta, size_t(n) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
     io.theta = p; p += nal;

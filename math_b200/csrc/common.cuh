@@ -166,10 +166,16 @@ struct DensityIO {
   int64_t n;
   const int* y; int y_vec; int y0;
   const double* theta; int theta_vec; double theta0;
+  // poisson_log: sum lgamma(n + 1) over all elements, computed once when the outcomes were cached (data only).  The
+  // elements poisson_log_lpmf.hpp:77 skips have n == 0, i.e. lgamma(1) = 0: the total needs no correction.
+  int lgamma_cached;
+  double lgamma_total;
   double* dtheta_row;         // per-element partials (vector operand) or null
   double* result;             // [5]: lp, sum dtheta, 0, witness, bits (1: outcome outside the support, 2: operand NaN, 4: LOG_ZERO)
 };
 int launch_density(const DensityIO& io, Workspace* ws, int device, cudaStream_t stream);
+int int_vector_stats(const int* d_y, int64_t n, int want_lgamma, cudaStream_t stream, double* lgamma_sum, int64_t* y_min,
+                     int64_t* y_max);
 
 // counters
 struct Counters {

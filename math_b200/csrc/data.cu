@@ -105,6 +105,35 @@ __global__ void y_stats_kernel(const int* __restrict__ y, int64_t n, int want_lg
   }
 }
 
+// min / max / sum lgamma(v + 1) of a device vector of ints (current device, synchronises the stream)
+int int_vector_stats(const int* d_y, int64_t n, int want_lgamma, cudaStream_t stream, double* lgamma_sum, int64_t* y_min,
+                     int64_t* y_max) {
+  const int nb = 256;
+  double* partial = nullptr;  // [nb] doubles followed by [2 * nb] ints
+  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&partial), nb * (sizeof(double) + 2 * sizeof(int))));
+  int* mm = reinterpret_cast<int*>(partial + nb);
+  y_stats_kernel<<<nb, 256, 0, stream>>>(d_y, n, want_lgamma, partial, mm);
+  double host[256];
+  int hmm[512];
+  cudaError_t e = cudaMemcpyAsync(host, partial, sizeof(host), cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(hmm, mm, sizeof(hmm), cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  cudaFree(partial);
+  SC_CUDA(e);
+  double s = 0.0;
+  int lo = INT_MAX, hi = INT_MIN;
+  for (int i = 0; i < nb; ++i) {
+    s += host[i];
+    lo = hmm[2 * i] < lo ? hmm[2 * i] : lo;
+    hi = hmm[2 * i + 1] > hi ? hmm[2 * i + 1] : hi;
+  }
+  if (lgamma_sum) *lgamma_sum = s;
+  if (y_min) *y_min = lo;
+  if (y_max) *y_max = hi;
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
+  return STAN_CUDA_OK;
+}
+
 static const size_t kStageBytes = size_t(256) << 20;  // staging buffer for the fill
 
 // Upload rows [row0, row0 + d->n) of the host matrix into d (already sized; d->t chosen).
@@ -202,30 +231,19 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
   d->lgamma_sum = 0.0;
   d->y_min = d->y_max = 0;
   if (!d->y_is_double) {
-    const int nb = 256;
-    double* partial = nullptr;  // [nb] doubles followed by [2 * nb] ints
-    SC_CUDA_CLEAN(cudaMalloc(reinterpret_cast<void**>(&partial), nb * (sizeof(double) + 2 * sizeof(int))));
-    int* mm = reinterpret_cast<int*>(partial + nb);
     const int want_lgamma = d->family == STAN_CUDA_POISSON_LOG || d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG;
-    y_stats_kernel<<<nb, 256, 0, stream>>>(static_cast<const int*>(d->y), n, want_lgamma, partial, mm);
-    double host[256];
-    int hmm[512];
-    cudaError_t e = cudaMemcpyAsync(host, partial, sizeof(host), cudaMemcpyDeviceToHost, stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(hmm, mm, sizeof(hmm), cudaMemcpyDeviceToHost, stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    cudaFree(partial);
-    SC_CUDA_CLEAN(e);
     double s = 0.0;
-    int lo = INT_MAX, hi = INT_MIN;
-    for (int i = 0; i < nb; ++i) {
-      s += host[i];
-      lo = hmm[2 * i] < lo ? hmm[2 * i] : lo;
-      hi = hmm[2 * i + 1] > hi ? hmm[2 * i + 1] : hi;
+    int64_t lo = 0, hi = 0;
+    {
+      const int rc_stats = int_vector_stats(static_cast<const int*>(d->y), n, want_lgamma, stream, &s, &lo, &hi);
+      if (rc_stats < 0) {
+        cleanup();
+        return rc_stats;
+      }
     }
     d->lgamma_sum = s;
     d->y_min = lo;
     d->y_max = hi;
-    counters().launches.fetch_add(1, std::memory_order_relaxed);
     // neg_binomial_2_log: histogram of y, so that sum lgamma(y + phi) and sum digamma(y + phi) cost
     // O(y_max) per evaluation instead of O(N) special-function calls in the hot loop
     if (d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG && lo >= 0 && hi < (1 << 20)) {

@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(THREADS) density_kernel(const DensityKernelPar
       const double yd = double(y);
       const double e = exp(th);                                                // :70-74
       if (!(th == -inf && y == 0)) {                                           // :77-86
-        if (lp_const) lp -= lgamma(yd + 1.0);
+        if (lp_const && !io.lgamma_cached) lp -= lgamma(yd + 1.0);
         if (lp_main) lp += yd * th - e;
       }
       d = yd - e;                                                              // :88-90
@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(THREADS) density_kernel(const DensityKernelPar
   if (threadIdx.x < 2) {
     double s = 0.0;
     for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.scratch + size_t(b) * 4 + threadIdx.x);
+    if (threadIdx.x == 0 && DENSITY == STAN_CUDA_DENSITY_POISSON_LOG && lp_const && io.lgamma_cached) s -= io.lgamma_total;
     io.result[threadIdx.x] = s;
     if (threadIdx.x == 0) {
       io.result[2] = 0.0;
