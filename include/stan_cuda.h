@@ -189,6 +189,7 @@ typedef struct stan_cuda_stats_t {
   uint64_t allreduces;       /* NCCL all-reduce calls */
   double last_fill_ms;       /* wall time of the most recent cache fill */
   uint64_t fused_allreduces; /* all-reduces done inside the fused kernel over peer memory */
+  uint64_t cache_evictions;  /* entries dropped to stay inside the cache budget */
 } stan_cuda_stats_t;
 
 /* ---- context -------------------------------------------------------------------------- */
@@ -237,6 +238,11 @@ STAN_CUDA_API void* stan_cuda_host_staging(size_t bytes);
 STAN_CUDA_API int stan_cuda_cache_invalidate(const void* host_ptr); /* drop entries keyed on this x (or y) pointer */
 STAN_CUDA_API void stan_cuda_cache_clear(void);
 STAN_CUDA_API int64_t stan_cuda_cache_bytes(void);                  /* device bytes held by the cache */
+/* Byte budget of the cache (all devices together): when a new data set does not fit, least-recently-used
+ * entries are dropped first (an evaluation that is still using one keeps it alive until it returns).
+ * 0 = automatic: 80 % of the smallest device's memory, or environment STAN_CUDA_CACHE_BYTES.
+ * (matrix_cl has no counterpart: its buffers live as long as the C++ object, stan/math/opencl/matrix_cl.hpp:32-454.) */
+STAN_CUDA_API void stan_cuda_cache_set_limit(int64_t bytes);
 
 /* ---- map_rect shard scope (thread-local) ---------------------------------------------------- */
 /* Inside a scope, evaluations of the calling thread run on `device` and their data is keyed by

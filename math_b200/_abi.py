@@ -100,6 +100,7 @@ class Stats(C.Structure):
         ("allreduces", C.c_uint64),
         ("last_fill_ms", C.c_double),
         ("fused_allreduces", C.c_uint64),
+        ("cache_evictions", C.c_uint64),
     ]
 
 
@@ -122,6 +123,7 @@ PROTOTYPES = {
     "stan_cuda_host_staging": (C.c_void_p, [C.c_size_t]),
     "stan_cuda_cache_invalidate": (C.c_int, [C.c_void_p]),
     "stan_cuda_cache_clear": (None, []),
+    "stan_cuda_cache_set_limit": (None, [C.c_int64]),
     "stan_cuda_cache_bytes": (C.c_int64, []),
     "stan_cuda_shard_scope_enter": (None, [C.c_int, C.c_int, C.c_int]),
     "stan_cuda_shard_scope_exit": (None, []),

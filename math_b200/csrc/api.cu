@@ -33,6 +33,7 @@ struct Entry {
   uint64_t fingerprint = 0;
   size_t bytes = 0;
   double lgamma_sum = 0.0;     // cached integer outcomes of a density: sum lgamma(v + 1)
+  uint64_t last_use = 0;       // tick of the most recent hit (LRU eviction under a byte budget)
   ~Entry() {
     for (Shard& s : shards) free_data_block(s.d);
     if (vec) {
@@ -47,6 +48,47 @@ typedef std::tuple<int, uintptr_t, uintptr_t, int64_t, int64_t, int64_t, int64_t
 
 static std::mutex g_cache_mu;
 static std::map<Key, std::shared_ptr<Entry>> g_cache;
+static uint64_t g_cache_tick = 0;       // guarded by g_cache_mu
+static int64_t g_cache_limit = 0;       // bytes; 0 = automatic (a fraction of the device memory)
+
+// Byte budget of the cache.  Data sets are immutable for the life of a Stan program, so the common case never
+// evicts; the budget keeps a long-lived process that keeps presenting NEW data (or a test-suite) from filling
+// the 180 GB of a B200.  Automatic budget: 80 % of the smallest device's memory.
+static int64_t cache_limit_locked() {
+  if (g_cache_limit > 0) return g_cache_limit;
+  static int64_t auto_limit = 0;
+  if (auto_limit == 0) {
+    const char* v = getenv("STAN_CUDA_CACHE_BYTES");
+    if (v && atoll(v) > 0) {
+      auto_limit = atoll(v);
+    } else {
+      int64_t smallest = 0;
+      for (int dev : context().devices) {
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess && (smallest == 0 || int64_t(prop.totalGlobalMem) < smallest))
+          smallest = int64_t(prop.totalGlobalMem);
+      }
+      auto_limit = smallest > 0 ? smallest / 5 * 4 : (int64_t(1) << 62);
+    }
+  }
+  return auto_limit;
+}
+
+// Drops least-recently-used entries until `incoming` more bytes fit the budget.  Entries are shared_ptr:
+// an evaluation that still holds one keeps its device memory until it returns.  Caller holds g_cache_mu.
+static void make_room_locked(int64_t incoming) {
+  const int64_t limit = cache_limit_locked();
+  int64_t total = incoming;
+  for (auto& kv : g_cache) total += int64_t(kv.second->bytes);
+  while (total > limit && !g_cache.empty()) {
+    auto lru = g_cache.begin();
+    for (auto it = g_cache.begin(); it != g_cache.end(); ++it)
+      if (it->second->last_use < lru->second->last_use) lru = it;
+    total -= int64_t(lru->second->bytes);
+    g_cache.erase(lru);
+    counters().cache_evictions.fetch_add(1, std::memory_order_relaxed);
+  }
+}
 
 struct Scope {
   bool active = false;
@@ -125,11 +167,13 @@ static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* ou
   auto it = g_cache.find(key);
   if (it != g_cache.end() && it->second->fingerprint == fp) {
     counters().cache_hits.fetch_add(1, std::memory_order_relaxed);
+    it->second->last_use = ++g_cache_tick;
     *out = it->second;
     return STAN_CUDA_OK;
   }
   counters().cache_misses.fetch_add(1, std::memory_order_relaxed);
   if (it != g_cache.end()) g_cache.erase(it);  // stale: same identity, different content
+  make_room_locked(a->n * ((a->k + 15) / 16 * 16 + 1) * int64_t(sizeof(double)));  // tiled x (padded) + y
   auto t0 = std::chrono::steady_clock::now();
   std::shared_ptr<Entry> e = std::make_shared<Entry>();
   e->fingerprint = fp;
@@ -151,6 +195,7 @@ static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* ou
   }
   auto t1 = std::chrono::steady_clock::now();
   counters().last_fill_ms.store(std::chrono::duration<double, std::milli>(t1 - t0).count());
+  e->last_use = ++g_cache_tick;
   g_cache[key] = e;
   *out = e;
   return STAN_CUDA_OK;
@@ -436,13 +481,16 @@ static int get_vec_entry(const double* v, int64_t n, int device, cudaStream_t st
   auto it = g_cache.find(key);
   if (it != g_cache.end() && it->second->fingerprint == fp) {
     counters().cache_hits.fetch_add(1, std::memory_order_relaxed);
+    it->second->last_use = ++g_cache_tick;
     *out = it->second;
     return STAN_CUDA_OK;
   }
   counters().cache_misses.fetch_add(1, std::memory_order_relaxed);
   if (it != g_cache.end()) g_cache.erase(it);
+  make_room_locked(n * int64_t(sizeof(double)));
   std::shared_ptr<Entry> e = std::make_shared<Entry>();
   e->fingerprint = fp;
+  e->last_use = ++g_cache_tick;
   e->vec_device = device;
   SC_CUDA(cudaSetDevice(device));
   SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->vec), size_t(n) * sizeof(double)));
@@ -550,13 +598,16 @@ static int get_ivec_entry(const int32_t* v, int64_t n, int device, int want_lgam
   auto it = g_cache.find(key);
   if (it != g_cache.end() && it->second->fingerprint == fp) {
     counters().cache_hits.fetch_add(1, std::memory_order_relaxed);
+    it->second->last_use = ++g_cache_tick;
     *out = it->second;
     return STAN_CUDA_OK;
   }
   counters().cache_misses.fetch_add(1, std::memory_order_relaxed);
   if (it != g_cache.end()) g_cache.erase(it);
+  make_room_locked(n * int64_t(sizeof(double)));
   std::shared_ptr<Entry> e = std::make_shared<Entry>();
   e->fingerprint = fp;
+  e->last_use = ++g_cache_tick;
   e->vec_device = device;
   const size_t bytes = ((size_t(n) + 1) & ~size_t(1)) * sizeof(int32_t);
   SC_CUDA(cudaSetDevice(device));
@@ -696,6 +747,12 @@ int stan_cuda_cache_invalidate(const void* host_ptr) {
 void stan_cuda_cache_clear(void) {
   std::lock_guard<std::mutex> lk(g_cache_mu);
   g_cache.clear();
+}
+
+void stan_cuda_cache_set_limit(int64_t bytes) {
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  g_cache_limit = bytes > 0 ? bytes : 0;
+  if (g_cache_limit > 0) make_room_locked(0);
 }
 
 int64_t stan_cuda_cache_bytes(void) {

@@ -180,7 +180,7 @@ int int_vector_stats(const int* d_y, int64_t n, int want_lgamma, cudaStream_t st
 // counters
 struct Counters {
   std::atomic<uint64_t> cache_hits{0}, cache_misses{0}, bytes_uploaded{0}, evals{0}, launches{0},
-      allreduces{0}, fused_allreduces{0};
+      allreduces{0}, fused_allreduces{0}, cache_evictions{0};
   std::atomic<double> last_fill_ms{0};
 };
 Counters& counters();

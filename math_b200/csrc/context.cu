@@ -222,6 +222,7 @@ int stan_cuda_stats(stan_cuda_stats_t* out) {
   out->allreduces = c.allreduces.load();
   out->last_fill_ms = c.last_fill_ms.load();
   out->fused_allreduces = c.fused_allreduces.load();
+  out->cache_evictions = c.cache_evictions.load();
   return STAN_CUDA_OK;
 }
 
@@ -234,6 +235,7 @@ void stan_cuda_stats_reset(void) {
   c.launches = 0;
   c.allreduces = 0;
   c.fused_allreduces = 0;
+  c.cache_evictions = 0;
   c.last_fill_ms = 0.0;
 }
 
