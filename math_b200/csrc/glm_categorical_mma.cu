@@ -49,25 +49,7 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                : "d"(a), "d"(b));
 }
 
-// exp(x) for x <= 0 (softmax terms exp(lin - max)), lean: x = n ln2 + r with |r| <= ln2 / 2, Taylor polynomial of
-// degree 13 in r (remainder below 5e-18), 2^n by an add into the exponent field.  Coefficients come from
-// the constant bank as DFMA operands: the libdevice exp spends more instructions on materialising its
-// constants and on the range checks this argument range does not need than on arithmetic (ncu: 64 % of the
-// kernel's instructions were the softmax phase).  x < -708 (a result below 1e-307 next to a sum >= 1) gives 0.
-__constant__ double kExpTaylor[14] = {1.0, 1.0, 1.0 / 2, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
-                                      1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600, 1.0 / 6227020800.0};
-__device__ __forceinline__ double exp_nonpos(double x) {
-  const double t = fma(x, 1.4426950408889634074, 6755399441055744.0);  // low word of t = rint(x / ln2)
-  const int n = __double2loint(t);
-  const double fn = t - 6755399441055744.0;
-  double r = fma(fn, -6.93147180369123816490e-01, x);  // ln2 split in two (fdlibm)
-  r = fma(fn, -1.90821492927058770002e-10, r);
-  double p = kExpTaylor[13];
-#pragma unroll
-  for (int i = 12; i >= 0; --i) p = fma(p, r, kExpTaylor[i]);
-  const double v = __hiloint2double(__double2hiint(p) + n * 1048576, __double2loint(p));
-  return x != x ? x : (x < -708.0 ? 0.0 : v);  // NaN (inf - inf) stays NaN: the caller's finiteness witness sees it
-}
+// (the softmax terms exp(lin - max) use exp_nonpos of glm_device.cuh)
 
 // NTL: n-tiles of 8 classes (1 | 2).  MPW: m-tiles of 8 columns per warp in phase B (1 | 2 | 4).
 // TPR: threads per row in phase S (4: 64 rows per tile, 8: 32 rows).  CPT: classes per thread in phase S,

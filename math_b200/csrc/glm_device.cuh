@@ -191,6 +191,50 @@ __device__ __forceinline__ void xchg_allreduce(const GlmKernelParams& p, double*
 }
 
 // ---------------------------------------------------------------------------------------------
+// Lean special functions for the argument ranges the epilogues actually use.  The libdevice exp / log1p spend
+// more instructions on materialising their constants (UMOV / IMAD.MOV pairs per coefficient) and on range
+// handling these call sites cannot reach than on arithmetic -- measured on the categorical kernel: 64 % of its
+// instructions were the softmax phase, 175 of 559 per thread and tile constant moves
+// (profiles/r01_cat_mma_*_details.txt).  Coefficients come from the constant bank as DFMA operands.
+// ---------------------------------------------------------------------------------------------
+static __constant__ double kExpTaylor[14] = {1.0, 1.0, 1.0 / 2, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040,
+                                             1.0 / 40320, 1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800,
+                                             1.0 / 479001600, 1.0 / 6227020800.0};
+static __constant__ double kAtanhOdd[11] = {1.0, 1.0 / 3, 1.0 / 5, 1.0 / 7, 1.0 / 9, 1.0 / 11, 1.0 / 13, 1.0 / 15,
+                                            1.0 / 17, 1.0 / 19, 1.0 / 21};
+
+// exp(x) for x <= 0: x = n ln2 + r with |r| <= ln2 / 2, Taylor polynomial of degree 13 in r (remainder below
+// 5e-18), 2^n by an add into the exponent field; <= 1 ulp against glibc on [-708, 0].  x < -708 (a result below
+// 1e-307) gives 0; NaN stays NaN (the callers' finiteness witnesses rely on it).
+__device__ __forceinline__ double exp_nonpos(double x) {
+  const double t = fma(x, 1.4426950408889634074, 6755399441055744.0);  // low word of t = rint(x / ln2)
+  const int n = __double2loint(t);
+  const double fn = t - 6755399441055744.0;
+  double r = fma(fn, -6.93147180369123816490e-01, x);  // ln2 split in two (fdlibm)
+  r = fma(fn, -1.90821492927058770002e-10, r);
+  double p = kExpTaylor[13];
+#pragma unroll
+  for (int i = 12; i >= 0; --i) p = fma(p, r, kExpTaylor[i]);
+  const double v = __hiloint2double(__double2hiint(p) + n * 1048576, __double2loint(p));
+  return x != x ? x : (x < -708.0 ? 0.0 : v);
+}
+
+// log1p(e) for 0 <= e <= 1 (e = exp(-|.|)): 1 + e = 2^k (1 + f) with k in {0, 1} and f in [-0.293, 0.414] formed
+// exactly, log1p(f) = 2 atanh(s), s = f / (2 + f), |s| <= 0.172: odd series up to s^21 (next term below 3e-17);
+// <= 2 ulp against glibc, exact 0 at 0, NaN stays NaN.
+__device__ __forceinline__ double log1p_unit(double e) {
+  const bool hi = e > 0.41421356237309503;
+  const double f = hi ? (e - 1.0) * 0.5 : e;
+  const double s = f / (2.0 + f);
+  const double z = s * s;
+  double r = kAtanhOdd[10];
+#pragma unroll
+  for (int i = 9; i >= 0; --i) r = fma(r, z, kAtanhOdd[i]);
+  const double l = 2.0 * s * r;
+  return hi ? (l + 1.90821492927058770002e-10) + 6.93147180369123816490e-01 : l;
+}
+
+// ---------------------------------------------------------------------------------------------
 // family epilogues: per-row log-likelihood terms and d = dL/deta, same expressions and the same
 // branch structure as the reference.
 // ---------------------------------------------------------------------------------------------
@@ -231,8 +275,8 @@ __device__ __forceinline__ RowTerms nb_row_epilogue(double eta, double alpha, do
   //   phi / (exp(theta) + phi)        = sigmoid(-u) = (u > 0 ? e : 1) / (1 + e)  (:185-190)
   const double u = theta - log_phi;
   const bool pos = u > 0.0;
-  const double e = exp(-fabs(u));
-  const double lse = (pos ? theta : log_phi) + log1p(e);
+  const double e = exp_nonpos(-fabs(u));
+  const double lse = (pos ? theta : log_phi) + log1p_unit(e);
   const double inv1pe = 1.0 / (1.0 + e);
   const double ypp = yv + phi;                                                // :127
   double q;                                                                   // (y + phi) / (exp(theta) + phi)
@@ -298,9 +342,9 @@ __device__ __forceinline__ RowTerms ordered_row_epilogue(double loc, int c, int 
   const double cut1 = loc - tab[0 * ncls + c - 1], cut2 = loc - tab[1 * ncls + c - 1];  // :124-125
   // exp(-|cut|) serves both the log-density (:128-131) and the derivative: for cut > 0 the reference
   // uses exp(-cut) / (1 + exp(-cut)), else 1 / (1 + exp(cut)) (:165-171) -- the same exponential
-  const double e1 = exp(-fabs(cut1)), e2 = exp(-fabs(cut2));
-  const double m1 = (cut1 > 0.0 ? -cut1 : 0.0) - log1p(e1);                          // :128-129
-  const double m2 = (cut2 <= 0.0 ? cut2 : 0.0) - log1p(e2);                          // :130-131
+  const double e1 = exp_nonpos(-fabs(cut1)), e2 = exp_nonpos(-fabs(cut2));
+  const double m1 = (cut1 > 0.0 ? -cut1 : 0.0) - log1p_unit(e1);                     // :128-129
+  const double m2 = (cut2 <= 0.0 ? cut2 : 0.0) - log1p_unit(e2);                     // :130-131
   o.t0 = c == 1 ? m1 : (c == ncls ? m2 : m2 + tab[4 * ncls + c - 1] + m1);            // :137-144
   const double ecd = tab[2 * ncls + c - 1], r = tab[3 * ncls + c - 1];
   const double s2 = (cut2 > 0 ? e2 : 1.0) / (1 + e2);                                 // :165-167
