@@ -1,7 +1,7 @@
 /* stan_cuda.h -- the C ABI of libstanmath_cuda.so (B200 / sm_100a).
  *
  * This is the drop-in boundary of the stan/math/cuda/ subsystem: plain C, plain pointers and
- * sizes, no Eigen / Stan / torch types.  The C++ host layer (stan/math/cuda/*.hpp) binds these
+ * sizes, no Eigen / Stan / torch types.  The C++ host layer (the headers under stan/math/cuda/) binds these
  * entry points from inside the reference's own function signatures; tests and bench.py bind
  * them through ctypes.  No exception crosses this boundary.
  *
@@ -18,6 +18,9 @@
  *                                  neg_binomial_2_log_glm_lpmf stan/math/prim/mat/prob/neg_binomial_2_log_glm_lpmf.hpp:108-197
  *                                  ordered_logistic_glm_lpmf   stan/math/prim/mat/prob/ordered_logistic_glm_lpmf.hpp:93-199
  *                                  categorical_logit_glm_lpmf  stan/math/prim/mat/prob/categorical_logit_glm_lpmf.hpp:74-190
+ *   stan_cuda_glm_eval_batch     the jobs of one map_rect call whose functor is a single GLM call, one launch per
+ *                                device; the per-job loop of
+ *                                  stan/math/rev/mat/functor/map_rect_concurrent.hpp:39-54
  *   stan_cuda_normal_lpdf_eval   the loop of normal_lpdf      stan/math/prim/scal/prob/normal_lpdf.hpp:67-110
  *   stan_cuda_density_eval       the loops of the vectorised elementwise densities
  *                                  bernoulli_logit_lpmf      stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
@@ -224,6 +227,12 @@ STAN_CUDA_API void stan_cuda_set_categorical_kernel(int variant);
 
 /* ---- host-level evaluation (what the Stan wrappers call) -------------------------------- */
 STAN_CUDA_API int stan_cuda_glm_eval(const stan_cuda_glm_args* a);
+/* `count` independent GLMs of one family (bernoulli_logit | poisson_log | normal_id) and one k, scalar alpha /
+ * sigma, in ONE kernel launch per device: item j runs on device j % device_count and its data is cached under
+ * (call_id, j), exactly like the jobs of map_rect (stan/math/rev/mat/functor/map_rect_concurrent.hpp:39-54 and
+ * stan_cuda_shard_scope_enter).  item_rc (optional, [count]) receives the per-item code; the return value is the
+ * worst of them (or a negative error, after which no output is valid). */
+STAN_CUDA_API int stan_cuda_glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int* item_rc);
 STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
 /* Returns STAN_CUDA_BAD_OPERAND when an outcome is outside the density's support (bernoulli_logit: not in
  * {0, 1}, bernoulli_logit_lpmf.hpp:42; poisson_log: negative, poisson_log_lpmf.hpp:38) or the operand is NaN

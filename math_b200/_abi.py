@@ -118,6 +118,7 @@ PROTOTYPES = {
     "stan_cuda_set_kernel": (None, [C.c_int]),
     "stan_cuda_set_categorical_kernel": (None, [C.c_int]),
     "stan_cuda_glm_eval": (C.c_int, [C.POINTER(GlmArgs)]),
+    "stan_cuda_glm_eval_batch": (C.c_int, [C.POINTER(GlmArgs), C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "stan_cuda_density_eval": (C.c_int, [C.POINTER(DensityArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
     "stan_cuda_host_staging": (C.c_void_p, [C.c_size_t]),

@@ -17,7 +17,7 @@
 #include <memory>
 #include <tuple>
 
-#include "context.cuh"
+#include "glm_device.cuh"
 
 namespace stancuda {
 
@@ -470,6 +470,158 @@ int glm_eval(const stan_cuda_glm_args* a) {
 }  // namespace stancuda
 
 // =============================================================================================
+// Batched evaluation: `count` independent GLMs of one family and one K (map_rect shards), item j on device
+// j % G (the dispatch rule of stan/math/cuda/map_rect_devices.hpp) and keyed (call_id, j) like a shard scope,
+// ONE kernel launch per device (glm_warp_batch_kernel, grid.y = items of that device).  SURVEY 8(e): "shards
+// resident on the same device should be evaluated by one batched launch when the functor is recognisably a
+// single GLM call".  A functor is opaque to map_rect, so the unmodified C++ path cannot know that; this entry
+// point is for callers that do (tests, bench tools, a code generator), and for measuring both ways.
+// =============================================================================================
+namespace stancuda {
+
+int glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int* item_rc) {
+  if (!items || count < 1) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval_batch: no items");
+  const int family = items[0].family;
+  if (family < STAN_CUDA_BERNOULLI_LOGIT || family > STAN_CUDA_NORMAL_ID)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval_batch: bernoulli_logit, poisson_log and normal_id only");
+  for (int i = 0; i < count; ++i) {
+    const stan_cuda_glm_args* a = &items[i];
+    SC_TRY(check_glm_args(a));
+    if (a->family != family || a->k != items[0].k || a->k < 1)
+      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval_batch: items must share family and k >= 1");
+    if (a->n < 1 || a->alpha_len != 1 || (family == STAN_CUDA_NORMAL_ID && a->sigma_len != 1) || (a->flags & STAN_CUDA_NEED_DY))
+      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval_batch: non-empty items with scalar alpha / sigma and data y only");
+    if (item_rc) item_rc[i] = STAN_CUDA_OK;
+  }
+  SC_TRY(ensure_init());
+  Context& c = context();
+  const int G = int(c.devices.size());
+  std::vector<std::shared_ptr<Entry>> ents;
+  ents.resize(size_t(count));
+  {
+    const Scope saved = tl_scope;
+    int rc = STAN_CUDA_OK;
+    for (int i = 0; i < count && rc >= 0; ++i) {
+      tl_scope.active = true;
+      tl_scope.call_id = call_id;
+      tl_scope.job = i;
+      tl_scope.device = i % G;
+      rc = get_glm_entry(&items[i], &ents[size_t(i)]);
+    }
+    tl_scope = saved;
+    SC_TRY(rc);
+  }
+  // eager domain check of the outcomes from the ranges computed at fill (bernoulli_logit_glm_lpmf.hpp:70,
+  // poisson_log_glm_lpmf.hpp:70): nothing is evaluated if any item fails
+  bool bad = false;
+  if (family != STAN_CUDA_NORMAL_ID) {
+    for (int i = 0; i < count; ++i) {
+      const stan_cuda_data* d = ents[size_t(i)]->shards[0].d;
+      if (d->y_min < 0 || (family == STAN_CUDA_BERNOULLI_LOGIT && d->y_max > 1)) {
+        bad = true;
+        if (item_rc) item_rc[i] = STAN_CUDA_BAD_OUTCOME;
+      }
+    }
+  }
+  if (bad) return STAN_CUDA_BAD_OUTCOME;
+
+  const int kpad = ents[0]->shards[0].d->t.kpad;
+  const size_t np = size_t(kpad) + 2, nr = size_t(kpad) + 4;
+  const size_t npa = (np + 1) & ~size_t(1), nra = (nr + 1) & ~size_t(1);
+  const size_t bs = (sizeof(GlmKernelParams) + 7) / 8;  // doubles per parameter block
+  struct DevRun {
+    ThreadDev* td = nullptr;
+    std::vector<int> idx;
+    double* h_res = nullptr;
+  };
+  std::vector<DevRun> runs;
+  runs.resize(size_t(G));
+  for (int i = 0; i < count; ++i) runs[size_t(i % G)].idx.push_back(i);
+  for (int g = 0; g < G; ++g) {
+    DevRun& run = runs[size_t(g)];
+    const int cnt = int(run.idx.size());
+    if (cnt == 0) continue;
+    const int dev = c.devices[size_t(g)];
+    SC_TRY(thread_dev(dev, &run.td));
+    ThreadDev* td = run.td;
+    SC_CUDA(cudaSetDevice(dev));
+    std::vector<const stan_cuda_data*> ds;
+    ds.resize(size_t(cnt));
+    int64_t min_tiles = INT64_MAX;
+    for (int j = 0; j < cnt; ++j) {
+      ds[size_t(j)] = ents[size_t(run.idx[size_t(j)])]->shards[0].d;
+      min_tiles = std::min(min_tiles, ds[size_t(j)]->t.tiles);
+    }
+    int gx = 1, gs = 1;
+    size_t scr = 0;
+    SC_TRY(glm_warp_batch_plan(ds[0], cnt, min_tiles, &gx, &gs, &scr));
+    const size_t scr_al = (scr + 1) & ~size_t(1);
+    const size_t tick_d = 32;  // 64 ticket words per problem
+    SC_TRY(td->reserve_dev(size_t(cnt) * (tick_d + scr_al + npa + nra + bs) + 8));
+    SC_TRY(td->reserve_host(size_t(cnt) * (npa + nra + bs) + 8));
+    double* dp = td->d_buf;
+    double* d_tick = dp; dp += size_t(cnt) * tick_d;
+    double* d_scr = dp; dp += size_t(cnt) * scr_al;
+    double* d_par = dp; dp += size_t(cnt) * npa;
+    double* d_res = dp; dp += size_t(cnt) * nra;
+    GlmKernelParams* d_batch = reinterpret_cast<GlmKernelParams*>(dp);
+    double* h_par = td->h_pinned;
+    run.h_res = h_par + size_t(cnt) * npa;
+    GlmKernelParams* h_batch = reinterpret_cast<GlmKernelParams*>(run.h_res + size_t(cnt) * nra);
+    SC_CUDA(cudaMemsetAsync(d_tick, 0, size_t(cnt) * tick_d * sizeof(double), td->stream));
+    std::vector<Workspace> wss;
+    wss.resize(size_t(cnt));  // views into d_buf: not owned, never freed through workspace_free
+    std::vector<LaunchIO> ios;
+    ios.reserve(size_t(cnt));
+    for (int j = 0; j < cnt; ++j) {
+      const stan_cuda_glm_args* a = &items[run.idx[size_t(j)]];
+      double* hp = h_par + size_t(j) * npa;
+      for (int q = 0; q < kpad; ++q) hp[q] = q < a->k ? a->beta[q] : 0.0;
+      hp[kpad] = a->alpha[0];
+      hp[kpad + 1] = family == STAN_CUDA_NORMAL_ID ? a->sigma[0] : 1.0;
+      Workspace& w = wss[size_t(j)];
+      w.device = dev;
+      w.scratch = d_scr + size_t(j) * scr_al;
+      w.ticket = reinterpret_cast<unsigned int*>(d_tick + size_t(j) * tick_d);
+      w.scratch_doubles = scr_al;
+      ios.push_back(LaunchIO{a->flags, d_par + size_t(j) * npa, nullptr, nullptr, d_res + size_t(j) * nra, nullptr, nullptr});
+    }
+    SC_CUDA(cudaMemcpyAsync(d_par, h_par, size_t(cnt) * npa * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    SC_TRY(launch_glm_warp_batch(ds.data(), ios.data(), wss.data(), cnt, gx, gs, h_batch, d_batch, td->stream));
+    SC_CUDA(cudaMemcpyAsync(run.h_res, d_res, size_t(cnt) * nra * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  }
+  int worst = STAN_CUDA_OK;
+  for (int g = 0; g < G; ++g) {
+    DevRun& run = runs[size_t(g)];
+    if (run.idx.empty()) continue;
+    SC_CUDA(cudaSetDevice(c.devices[size_t(g)]));
+    SC_CUDA(cudaStreamSynchronize(run.td->stream));
+    for (size_t j = 0; j < run.idx.size(); ++j) {
+      const stan_cuda_glm_args* a = &items[run.idx[j]];
+      const double* res = run.h_res + j * nra;
+      if (a->lp) *a->lp = res[0];
+      if ((a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) memcpy(a->dbeta, res + 4, size_t(a->k) * sizeof(double));
+      if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha) a->dalpha[0] = res[1];
+      if ((a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma && family == STAN_CUDA_NORMAL_ID) a->dsigma[0] = res[2];
+      if (a->aux) {
+        a->aux[0] = res[1];
+        a->aux[1] = res[3];
+        a->aux[2] = 0.0;
+        a->aux[3] = ents[size_t(run.idx[j])]->shards[0].d->lgamma_sum;
+      }
+      if (!isfinite(res[3])) {
+        worst = STAN_CUDA_NONFINITE;
+        if (item_rc) item_rc[run.idx[j]] = STAN_CUDA_NONFINITE;
+      }
+    }
+  }
+  counters().evals.fetch_add(uint64_t(count), std::memory_order_relaxed);
+  return worst;
+}
+
+}  // namespace stancuda
+
+// =============================================================================================
 // normal_lpdf
 // =============================================================================================
 namespace stancuda {
@@ -724,6 +876,9 @@ using namespace stancuda;
 extern "C" {
 
 int stan_cuda_glm_eval(const stan_cuda_glm_args* a) { return glm_eval(a); }
+int stan_cuda_glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int* item_rc) {
+  return glm_eval_batch(items, count, call_id, item_rc);
+}
 int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) { return normal_lpdf_eval(a); }
 int stan_cuda_density_eval(const stan_cuda_density_args* a) { return density_eval(a); }
 void* stan_cuda_host_staging(size_t bytes) { return host_staging(bytes); }

@@ -57,6 +57,11 @@ __device__ __forceinline__ double kernel_param(const GlmKernelParams& p, int i) 
 }
 
 int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, GlmKernelParams* p);
+// batched launch (glm_warp.cu): plan the grid, then launch `count` problems of one device in one kernel
+int glm_warp_batch_plan(const stan_cuda_data* d0, int count, int64_t min_tiles, int* grid_x, int* group_size,
+                        size_t* scratch_doubles_per_problem);
+int launch_glm_warp_batch(const stan_cuda_data* const* ds, const LaunchIO* ios, Workspace* wss, int count, int grid_x,
+                          int group_size, GlmKernelParams* h_batch, const GlmKernelParams* d_batch, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------
 // PTX helpers: mbarrier + 1-D TMA bulk copy (SASS: UBLKCP / SYNCS)

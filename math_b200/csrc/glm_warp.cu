@@ -43,8 +43,11 @@ __device__ __forceinline__ void consumer_sync() { __syncthreads(); }
 // PAIR (needs FULLKC and C >= 2): two tiles per iteration; the even column-group lanes of a row evaluate
 // the epilogue of tile A's row, the odd ones tile B's, `d` is exchanged by shuffle and x is re-read from
 // the still-resident stages for the gradient FMAs -- the epilogue runs C/2 instead of C times per row.
+// The body is shared by two entry points: glm_warp_kernel (one problem, parameter block by value in the kernel
+// arguments) and glm_warp_batch_kernel (blockIdx.y selects one of several independent problems whose parameter
+// blocks sit in device memory: map_rect shards of one device in ONE launch).
 template <int FAMILY, bool ROWIO, bool FULLKC, bool PAIR>
-__global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKernelParams p) {
+__device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr int NT = kWarpConsumers * 32;
   const int tid = threadIdx.x;
@@ -352,6 +355,18 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKern
   finish_reduction<FAMILY, NT>(p, tid, cols, part, fin, &s_flag, [] { consumer_sync(); });
 }
 
+template <int FAMILY, bool ROWIO, bool FULLKC, bool PAIR>
+__global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_kernel(const GlmKernelParams p) {
+  glm_warp_body<FAMILY, ROWIO, FULLKC, PAIR>(p);
+}
+
+// grid = (CTAs per problem, problems): every problem has its own scratch, tickets and result block, and
+// gridDim.x / blockIdx.x mean inside the body what they mean in a single launch.
+template <int FAMILY, bool FULLKC, bool PAIR>
+__global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_batch_kernel(const GlmKernelParams* __restrict__ batch) {
+  glm_warp_body<FAMILY, false, FULLKC, PAIR>(batch[blockIdx.y]);
+}
+
 // =============================================================================================
 // host side
 // =============================================================================================
@@ -521,6 +536,98 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
       return launch_warp_inst<STAN_CUDA_ORDERED_LOGISTIC, false>(p, grid, smem, stream);
   }
   return fail(STAN_CUDA_ERR_ARG, "launch_glm: unknown family");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Batched launch: `count` independent problems of one family and one tile shape on one device in ONE launch
+// (grid.y = count).  The caller provides, per problem, a scratch / ticket / result region through the
+// Workspace array `wss` (tickets zeroed), pinned host memory for the parameter blocks (h_batch) and its
+// device copy (d_batch).  Scalar intercepts only (no per-row operands), families bernoulli_logit /
+// poisson_log / normal_id, no exchange.
+// ---------------------------------------------------------------------------------------------
+template <int FAMILY>
+static int launch_warp_batch_family(bool fullkc, bool pair, const GlmKernelParams* d_batch, dim3 grid, size_t smem,
+                                    cudaStream_t stream) {
+  // (the three kernels share one function-pointer type, so the shared-memory opt-in is tracked per variant)
+  auto go = [&](auto kern, int variant) -> int {
+    static std::atomic<size_t> configured[3][64];
+    int dev = 0;
+    SC_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && configured[variant][dev].load(std::memory_order_relaxed) < smem) {
+      SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      configured[variant][dev].store(smem, std::memory_order_relaxed);
+    }
+    kern<<<grid, kWarpThreads, smem, stream>>>(d_batch);
+    SC_CUDA(cudaGetLastError());
+    counters().launches.fetch_add(1, std::memory_order_relaxed);
+    return STAN_CUDA_OK;
+  };
+  if (pair) return go(glm_warp_batch_kernel<FAMILY, true, true>, 0);
+  if (fullkc) return go(glm_warp_batch_kernel<FAMILY, true, false>, 1);
+  return go(glm_warp_batch_kernel<FAMILY, false, false>, 2);
+}
+
+int glm_warp_batch_plan(const stan_cuda_data* d0, int count, int64_t min_tiles, int* grid_x, int* group_size,
+                        size_t* scratch_doubles_per_problem) {
+  const Tiling& t = d0->t;
+  if (t.layout != kLayoutWarp) return fail(STAN_CUDA_ERR_ARG, "glm batch: needs the warp tile layout");
+  const int sms = sm_count(d0->device);
+  int64_t gx = (int64_t(sms) * 2) / (count > 0 ? count : 1);  // one wave of 2 CTAs per SM over all problems
+  if (gx < 1) gx = 1;
+  if (gx > min_tiles) gx = min_tiles;
+  int gs = 1;
+  while (gs * gs < gx) ++gs;
+  const int ngroups = int((gx + gs - 1) / gs);
+  if (ngroups > 60) return fail(STAN_CUDA_ERR_ARG, "glm batch: grid too large for the ticket block");
+  *grid_x = int(gx);
+  *group_size = gs;
+  *scratch_doubles_per_problem = size_t(gx + ngroups) * (size_t(t.kpad) + 4) + 2;
+  return STAN_CUDA_OK;
+}
+
+int launch_glm_warp_batch(const stan_cuda_data* const* ds, const LaunchIO* ios, Workspace* wss, int count, int grid_x,
+                          int group_size, GlmKernelParams* h_batch, const GlmKernelParams* d_batch, cudaStream_t stream) {
+  if (count < 1) return fail(STAN_CUDA_ERR_ARG, "glm batch: empty");
+  const Tiling& t0 = ds[0]->t;
+  const int family = ds[0]->family;
+  if (family > STAN_CUDA_NORMAL_ID) return fail(STAN_CUDA_ERR_ARG, "glm batch: bernoulli_logit, poisson_log and normal_id only");
+  const int sms = sm_count(ds[0]->device);
+  (void)sms;
+  const size_t budget = (size_t(228) * 1024) / 2 - 1024 - 64;
+  int stages = 6;
+  size_t stage_bytes = 0;
+  while (stages > 2 && warp_smem_bytes(t0, stages, 0, nullptr) > budget) --stages;
+  size_t smem = warp_smem_bytes(t0, stages, 0, &stage_bytes);
+  while (stages > 1 && smem > size_t(227) * 1024) smem = warp_smem_bytes(t0, --stages, 0, &stage_bytes);
+  if (smem > size_t(227) * 1024) return fail(STAN_CUDA_ERR_ARG, "glm batch: tile does not fit shared memory");
+  const bool pair = pair_mode(t0) && stages >= 3;
+  for (int i = 0; i < count; ++i) {
+    const stan_cuda_data* d = ds[i];
+    const Tiling& t = d->t;
+    if (d->family != family || d->device != ds[0]->device || t.layout != kLayoutWarp || t.C != t0.C || t.kc != t0.kc ||
+        t.R != t0.R || t.kpad != t0.kpad || d->y_is_double != ds[0]->y_is_double)
+      return fail(STAN_CUDA_ERR_ARG, "glm batch: problems must share family, device and tile shape");
+    if (d->n <= 0 || t.tiles < grid_x) return fail(STAN_CUDA_ERR_ARG, "glm batch: a problem has fewer tiles than CTAs");
+    if (ios[i].d_alpha_vec || ios[i].d_sigma_vec || ios[i].d_row_dalpha || ios[i].d_row_dsigma || ios[i].xchg)
+      return fail(STAN_CUDA_ERR_ARG, "glm batch: scalar intercept / scale only, no exchange");
+    GlmKernelParams* p = &h_batch[i];
+    SC_TRY(fill_kernel_params(d, ios[i], &wss[i], p));
+    p->stages = stages;
+    p->group_size = group_size;
+    p->stage_bytes = uint32_t(stage_bytes);
+    p->blocked = tuning().blocked;
+    p->ord_private = 0;
+    p->pair = pair ? 1 : 0;
+  }
+  SC_CUDA(cudaMemcpyAsync(const_cast<GlmKernelParams*>(d_batch), h_batch, size_t(count) * sizeof(GlmKernelParams),
+                          cudaMemcpyHostToDevice, stream));
+  const dim3 grid(unsigned(grid_x), unsigned(count), 1);
+  const bool fullkc = t0.kc == kMaxKc;
+  switch (family) {
+    case STAN_CUDA_BERNOULLI_LOGIT: return launch_warp_batch_family<STAN_CUDA_BERNOULLI_LOGIT>(fullkc, pair, d_batch, grid, smem, stream);
+    case STAN_CUDA_POISSON_LOG: return launch_warp_batch_family<STAN_CUDA_POISSON_LOG>(fullkc, pair, d_batch, grid, smem, stream);
+    default: return launch_warp_batch_family<STAN_CUDA_NORMAL_ID>(fullkc, pair, d_batch, grid, smem, stream);
+  }
 }
 
 }  // namespace stancuda

@@ -421,6 +421,57 @@ def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
     return float(lp[0]), grads
 
 
+class GlmBatch:
+    """`count` independent GLMs of one family and one K evaluated with ONE kernel launch per device
+    (stan_cuda_glm_eval_batch): the jobs of a map_rect call whose functor is a single GLM call.
+    The argument blocks are built once; `eval(alphas, betas, sigmas)` only rewrites the parameters."""
+
+    def __init__(self, family, xs, ys, call_id=0, flags=None):
+        fam = _abi.FAMILIES[family] if isinstance(family, str) else family
+        self.fam, self.count, self.call_id = fam, len(xs), call_id
+        self.args = (_abi.GlmArgs * self.count)()
+        self.keep, self.k = [], None
+        if flags is None:
+            flags = glm_flags(fam, False)
+        for j, (x, y) in enumerate(zip(xs, ys)):
+            x, row_major, ldx = _prep_x(x)
+            n, k = x.shape
+            self.k = k if self.k is None else self.k
+            y = _f64(y) if fam == _abi.NORMAL_ID else np.ascontiguousarray(np.asarray(y, dtype=np.int32))
+            bufs = {"alpha": np.zeros(1), "beta": np.zeros(k), "sigma": np.ones(1), "lp": np.zeros(1), "dbeta": np.zeros(k),
+                    "dalpha": np.zeros(1), "dsigma": np.zeros(1)}
+            a = self.args[j]
+            a.family, a.flags, a.n, a.k = fam, flags, n, k
+            a.x, a.ldx, a.x_row_major = x.ctypes.data, ldx, row_major
+            a.y, a.y_is_double = y.ctypes.data, int(fam == _abi.NORMAL_ID)
+            a.alpha, a.alpha_len, a.beta = bufs["alpha"].ctypes.data, 1, bufs["beta"].ctypes.data
+            if fam in _abi.HAS_SCALE:
+                a.sigma, a.sigma_len = bufs["sigma"].ctypes.data, 1
+            a.lp, a.dbeta, a.dalpha, a.dsigma = (bufs["lp"].ctypes.data, bufs["dbeta"].ctypes.data,
+                                                 bufs["dalpha"].ctypes.data, bufs["dsigma"].ctypes.data)
+            self.keep.append((x, y, bufs))
+        self.item_rc = (C.c_int * self.count)()
+
+    def eval(self, alphas, betas, sigmas=None):
+        """alphas: (count,), betas: (count, k) or (k,) shared, sigmas: (count,) -> list of result dicts."""
+        betas = np.asarray(betas, float)
+        for j, (_, _, b) in enumerate(self.keep):
+            b["alpha"][0] = alphas[j]
+            b["beta"][:] = betas if betas.ndim == 1 else betas[j]
+            if sigmas is not None:
+                b["sigma"][0] = sigmas[j]
+        rc = self.call()
+        return rc, self.results()
+
+    def call(self):
+        """The C-ABI call alone, with the parameters last written by eval()."""
+        return check(lib().stan_cuda_glm_eval_batch(self.args, self.count, self.call_id, self.item_rc))
+
+    def results(self):
+        return [{"rc": self.item_rc[j], "lp": float(b["lp"][0]), "dbeta": b["dbeta"].copy(), "dalpha": b["dalpha"].copy(),
+                     "dsigma": b["dsigma"].copy()} for j, (_, _, b) in enumerate(self.keep)]
+
+
 def density_eval(density, n, theta, flags):
     """Raw C-ABI call stan_cuda_density_eval; dict with rc, lp, dtheta (theta's shape)."""
     d = _abi.DENSITIES[density] if isinstance(density, str) else density
