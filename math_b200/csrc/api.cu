@@ -107,10 +107,14 @@ static uint64_t fnv(uint64_t h, uint64_t v) {
 // Content fingerprint from <= 64 sampled elements of each array: catches an address that is
 // reused for different data (the reference once reverted a transparent GPU cache for
 // exactly this reason, RELEASE-NOTES.txt:36).
-static uint64_t fingerprint_glm(const stan_cuda_glm_args* a) {
+// `samples` elements of each array.  Host-pointer keys use 64: an address can be reused for other data.  Inside a
+// map_rect shard scope the identity is (call_id, job) and immutability is map_rect's own contract
+// (stan/math/prim/mat/functor/map_rect.hpp:97-100), so 4 samples per array (first, last, two in between) remain as
+// a tripwire only: the 128 scattered host reads per evaluation cost more than the launch of a 26 MB shard.
+static uint64_t fingerprint_glm(const stan_cuda_glm_args* a, int64_t samples) {
   uint64_t h = 1469598103934665603ull;
   const int64_t cnt = a->n * a->k;
-  const int64_t step = cnt > 64 ? cnt / 64 : 1;
+  const int64_t step = cnt > samples ? (cnt - 1) / (samples - 1) : 1;
   for (int64_t q = 0; q < cnt; q += step) {
     int64_t i, j;
     if (a->x_row_major) { i = q / a->k; j = q % a->k; } else { j = q / a->n; i = q % a->n; }
@@ -119,7 +123,7 @@ static uint64_t fingerprint_glm(const stan_cuda_glm_args* a) {
     memcpy(&bits, &v, 8);
     h = fnv(h, bits);
   }
-  const int64_t ystep = a->n > 64 ? a->n / 64 : 1;
+  const int64_t ystep = a->n > samples ? (a->n - 1) / (samples - 1) : 1;
   for (int64_t i = 0; i < a->n; i += ystep) {
     uint64_t bits = 0;
     if (a->y_is_double) memcpy(&bits, static_cast<const double*>(a->y) + i, 8);
@@ -162,7 +166,7 @@ static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* ou
     key = Key(0, uintptr_t(a->x), uintptr_t(a->y), a->n, a->k, a->ldx,
               int64_t(a->family) * 4 + a->x_row_major * 2 + a->y_is_double + 64 * tuning().layout + 256 * tuning().cat_mma);
   }
-  const uint64_t fp = fingerprint_glm(a);
+  const uint64_t fp = fingerprint_glm(a, tl_scope.active ? 4 : 64);
   std::lock_guard<std::mutex> lk(g_cache_mu);
   auto it = g_cache.find(key);
   if (it != g_cache.end() && it->second->fingerprint == fp) {
