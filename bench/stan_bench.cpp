@@ -340,7 +340,7 @@ double int_density_once(const std::vector<int>& y, const VectorXd& th_val, Resul
 }
 
 struct Timing {
-  double median = 0, best = 0;
+  double median = 0, best = 0, p10 = 0, p90 = 0;
   int reps = 0;
 };
 
@@ -358,12 +358,15 @@ Timing time_reps(int warm, int reps, double budget_s, F&& f) {
   r.reps = int(t.size());
   r.best = t.front();
   r.median = t[t.size() / 2];
+  r.p10 = t[size_t(0.1 * double(t.size() - 1) + 0.5)];
+  r.p90 = t[size_t(0.9 * double(t.size() - 1) + 0.5)];
   return r;
 }
 
 void print_timing(const char* name, const Timing& t) {
-  std::printf("\"%s\": {\"evals_per_s\": %.6g, \"median_ms\": %.6g, \"best_ms\": %.6g, \"reps\": %d}", name,
-              1.0 / t.median, t.median * 1e3, t.best * 1e3, t.reps);
+  std::printf("\"%s\": {\"evals_per_s\": %.6g, \"median_ms\": %.6g, \"p10_ms\": %.6g, \"p90_ms\": %.6g, \"best_ms\": %.6g, "
+              "\"reps\": %d}",
+              name, 1.0 / t.median, t.median * 1e3, t.p10 * 1e3, t.p90 * 1e3, t.best * 1e3, t.reps);
 }
 
 }  // namespace
