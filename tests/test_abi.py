@@ -89,3 +89,21 @@ def test_host_wrapper_error_contract_without_device():
     with pytest.raises(glm.DomainError):
         glm.normal_lpdf([0.0], [0.0], [0.0])
     assert glm.normal_lpdf([], [0.0], [1.0])[0] == 0.0
+
+
+def test_header_is_plain_c():
+    """The drop-in boundary is a C ABI: include/stan_cuda.h must compile as C99 without any C++ or CUDA header."""
+    import shutil
+    import subprocess
+    import tempfile
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if not cc:
+        pytest.skip("no C compiler")
+    with tempfile.TemporaryDirectory() as d:
+        src = os.path.join(d, "t.c")
+        with open(src, "w") as f:
+            f.write('#include "stan_cuda.h"\nint main(void) { stan_cuda_glm_args a; stan_cuda_density_args b; '
+                    '(void)a; (void)b; return sizeof(stan_cuda_stats_t) == 72 ? 0 : 1; }\n')
+        r = subprocess.run([cc, "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), "-c", src,
+                            "-o", os.path.join(d, "t.o")], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        assert r.returncode == 0, r.stdout
