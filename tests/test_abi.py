@@ -107,3 +107,14 @@ def test_header_is_plain_c():
         r = subprocess.run([cc, "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), "-c", src,
                             "-o", os.path.join(d, "t.o")], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert r.returncode == 0, r.stdout
+
+
+def test_cxx_routing_table_compiles_and_runs_without_a_gpu():
+    """test/unit/math/cuda/routing_static_test.cpp: static_asserts over the eligibility traits (which instantiations
+    of the reference's templates go to the device) plus two calls that must stay on the reference loop."""
+    import subprocess
+    exe = os.path.join(ROOT, "build", "cxx", "cuda_routing_static_test")
+    if not os.path.exists(exe):
+        pytest.skip("not built (test/Makefile needs /root/reference)")
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+    assert r.returncode == 0 and "PASSED" in r.stdout, r.stdout
