@@ -545,6 +545,7 @@ int glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int*
     DevRun& run = runs[size_t(g)];
     const int cnt = int(run.idx.size());
     if (cnt == 0) continue;
+    if (cnt > 65535) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval_batch: more than 65535 items per device (grid.y)");
     const int dev = c.devices[size_t(g)];
     SC_TRY(thread_dev(dev, &run.td));
     ThreadDev* td = run.td;
