@@ -417,6 +417,12 @@ def test_full_size_c3_row_additivity_and_sample_parity(glm, L, request):
     n, k = 10_000_000, 128
     x, y, alpha, beta, _ = synth_shard("poisson_log", n, k, seed=1003)
     full = _raw_eval(glm, _abi.POISSON_LOG, x.ctypes.data, n, n, k, y.ctypes.data, alpha[0], beta)
+    from tests import config_cases as cc
+    golden, man = cc.load()                      # outputs of the compiled reference on these same inputs
+    if cc.inputs_reproduce(man, "c3", x, y):
+        assert_close(full[0], golden["c3/lp"][0], "C3 lp vs compiled reference")
+        assert_close(full[1], golden["c3/dbeta"], "C3 dbeta vs compiled reference")
+        assert_close(full[2], golden["c3/dalpha"][0], "C3 dalpha vs compiled reference")
     cuts = [0, 3_333_337, 3_333_337 + 4_096_001, n]
     parts = [_raw_eval(glm, _abi.POISSON_LOG, x.ctypes.data + 8 * r0, n, r1 - r0, k, y.ctypes.data + 4 * r0, alpha[0], beta)
              for r0, r1 in zip(cuts[:-1], cuts[1:])]
