@@ -32,6 +32,15 @@ from tests.config_cases import (C1, C5, CONFIGS, GOLDEN_DIR, c1_inputs, c5_shard
 from tests.helpers import rel_err  # noqa: E402
 
 
+REF_HEADERS = ["stan/math/version.hpp", "stan/math/prim/mat/prob/bernoulli_logit_glm_lpmf.hpp",
+               "stan/math/prim/mat/prob/poisson_log_glm_lpmf.hpp", "stan/math/prim/mat/prob/normal_id_glm_lpdf.hpp",
+               "stan/math/prim/scal/prob/normal_lpdf.hpp", "stan/math/rev/mat/functor/map_rect_concurrent.hpp"]
+
+
+def reference_state(root="/root/reference"):
+    return {h: hashlib.sha256(open(os.path.join(root, h), "rb").read()).hexdigest()[:16] for h in REF_HEADERS}
+
+
 def main():
     import torch
     out, man = {}, {"generator": "bench.synth_shard (torch CPU generator)", "configs": {}}
@@ -39,6 +48,7 @@ def main():
     man["numpy"] = np.__version__
     man["host"] = platform.platform()
     man["reference"] = L.ref_lib().stanref_version().decode()
+    man["reference_sources_sha256"] = reference_state()      # /root/reference is not a git checkout: hash the path's headers
     man["compiler"] = subprocess.run(["g++", "--version"], stdout=subprocess.PIPE, text=True).stdout.splitlines()[0]
     for name in CONFIGS:
         t0 = time.time()
