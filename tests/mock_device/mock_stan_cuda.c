@@ -1,0 +1,126 @@
+/* tests/mock_device/mock_stan_cuda.c -- TEST DOUBLE of libstanmath_cuda.so.  TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * The CPU suite (`pytest -m "not gpu"`) has no GPU, and the product library has no CPU path: every
+ * stan_cuda_*_eval fails loudly without a device.  To exercise the C++ HOST LAYER on CPU all the same -- the
+ * include-path overlay and its routing, argument marshalling (stan/math/cuda/marshal.hpp), the mapping of ABI
+ * return codes onto the reference's exceptions, the assembly of the tape node from the returned partials,
+ * map_rect's shard scopes -- tests/test_cxx_mock_cpu.py runs the C++ test binaries (the reference's own unit
+ * tests compiled against the overlay, test/unit/math/cuda) with THIS library in front of them on
+ * LD_LIBRARY_PATH.  It implements the entry points those binaries import by forwarding the argument structs to
+ * the plain-C oracle (oracle/glm_oracle.c, whose functions take the very same structs) and adds the return-code
+ * contract of include/stan_cuda.h that lives in the product's host code rather than in the oracle
+ * (STAN_CUDA_BAD_OUTCOME from the outcome range, STAN_CUDA_BAD_OPERAND for normal_lpdf).
+ *
+ * It is built into build/mock/ by the test that uses it, is never installed, never on the product's library
+ * path, never loaded by a `-m gpu` test, by smoke() or by bench.py.  What it proves is the host layer, not the
+ * kernels: the GPU parity tests run the same binaries against the real library.
+ */
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/stan_cuda.h"
+
+int oracle_glm_eval(const stan_cuda_glm_args* a);
+int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a);
+int oracle_density_eval(const stan_cuda_density_args* a);
+
+static __thread char tl_error[256];
+static __thread int tl_scope_active, tl_scope_call, tl_scope_job, tl_scope_device;
+static unsigned long long g_evals, g_scoped_evals, g_invalidations;
+
+static int fail(int rc, const char* what) {
+  snprintf(tl_error, sizeof tl_error, "mock device: %s", what);
+  return rc;
+}
+
+int stan_cuda_init(int n_devices) { (void)n_devices; return STAN_CUDA_OK; }
+int stan_cuda_device_count(void) {
+  const char* v = getenv("STAN_CUDA_MOCK_DEVICES");   /* lets a test see map_rect's job -> device dispatch */
+  return v && atoi(v) > 0 ? atoi(v) : 1;
+}
+const char* stan_cuda_describe(void) { return "mock device (tests/mock_device): C ABI forwarded to the plain-C oracle"; }
+const char* stan_cuda_last_error(void) { return tl_error; }
+
+int stan_cuda_stats(stan_cuda_stats_t* out) {
+  if (!out) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_stats: null");
+  memset(out, 0, sizeof *out);
+  out->evals = g_evals;
+  out->cache_hits = g_scoped_evals;        /* the mock's meaning: evaluations that ran inside a shard scope */
+  out->cache_misses = g_invalidations;     /* the mock's meaning: stan_cuda_cache_invalidate calls */
+  return STAN_CUDA_OK;
+}
+
+/* include/stan_cuda.h, code 2: the product answers the eager outcome check from the range computed at cache fill */
+static int outcome_out_of_range(const stan_cuda_glm_args* a) {
+  if (a->family == STAN_CUDA_NORMAL_ID || a->y_is_double) return 0;
+  const int32_t* y = (const int32_t*)a->y;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const int64_t v = y[i];
+    switch (a->family) {
+      case STAN_CUDA_BERNOULLI_LOGIT: if (v < 0 || v > 1) return 1; break;
+      case STAN_CUDA_ORDERED_LOGISTIC: if (v < 1 || v > a->cuts_len + 1) return 1; break;
+      case STAN_CUDA_CATEGORICAL_LOGIT: if (v < 1 || v > a->n_classes) return 1; break;
+      default: if (v < 0) return 1; break;
+    }
+  }
+  return 0;
+}
+
+int stan_cuda_glm_eval(const stan_cuda_glm_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null args");
+  if (a->n > 0 && (!a->y || (!a->x && a->k > 0))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null x or y");
+  if (outcome_out_of_range(a)) return STAN_CUDA_BAD_OUTCOME;
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  if (tl_scope_active) __atomic_fetch_add(&g_scoped_evals, 1, __ATOMIC_RELAXED);
+  const int rc = oracle_glm_eval(a);
+  return rc < 0 ? fail(rc, "stan_cuda_glm_eval: bad argument") : rc;
+}
+
+int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: null args");
+  /* include/stan_cuda.h, code 3: y NaN, mu not finite, sigma not > 0 (normal_lpdf.hpp:51-53) */
+  for (int64_t i = 0; i < a->y_len; ++i) if (isnan(a->y[i])) return STAN_CUDA_BAD_OPERAND;
+  for (int64_t i = 0; i < a->mu_len; ++i) if (!isfinite(a->mu[i])) return STAN_CUDA_BAD_OPERAND;
+  for (int64_t i = 0; i < a->sigma_len; ++i) if (!(a->sigma[i] > 0.0)) return STAN_CUDA_BAD_OPERAND;
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  const int rc = oracle_normal_lpdf_eval(a);
+  return rc < 0 ? fail(rc, "stan_cuda_normal_lpdf_eval: bad argument") : rc;
+}
+
+int stan_cuda_density_eval(const stan_cuda_density_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: null args");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  const int rc = oracle_density_eval(a);
+  return rc < 0 ? fail(rc, "stan_cuda_density_eval: bad argument") : rc;
+}
+
+/* the product returns pinned memory of the calling thread; pageable memory serves a host-only run */
+void* stan_cuda_host_staging(size_t bytes) {
+  static __thread void* p;
+  static __thread size_t cap;
+  if (bytes > cap) {
+    free(p);
+    cap = bytes + bytes / 4 + 4096;
+    p = malloc(cap);
+    if (!p) cap = 0;
+  }
+  return p;
+}
+
+int stan_cuda_cache_invalidate(const void* host_ptr) {
+  (void)host_ptr;
+  __atomic_fetch_add(&g_invalidations, 1, __ATOMIC_RELAXED);
+  return 0;
+}
+void stan_cuda_cache_clear(void) {}
+int64_t stan_cuda_cache_bytes(void) { return 0; }
+
+void stan_cuda_shard_scope_enter(int call_id, int job, int device) {
+  tl_scope_active = 1;
+  tl_scope_call = call_id;
+  tl_scope_job = job;
+  tl_scope_device = device;
+}
+void stan_cuda_shard_scope_exit(void) { tl_scope_active = 0; }

@@ -26,7 +26,13 @@ def test_cxx_binary(name):
     exe = os.path.join(CXX_DIR, name)
     if not os.path.exists(exe):
         pytest.skip("%s not built (test/Makefile needs /root/reference)" % name)
-    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    env = dict(os.environ)    # the real library, through RUNPATH: never the CPU suite's test double (build/mock)
+    env["LD_LIBRARY_PATH"] = os.pathsep.join(p for p in env.get("LD_LIBRARY_PATH", "").split(os.pathsep)
+                                             if p and os.path.join("build", "mock") not in p)
+    ldd = subprocess.run(["ldd", exe], stdout=subprocess.PIPE, text=True, env=env).stdout
+    if "libstanmath_cuda.so" in ldd:   # (tests whose argument kinds never route to the device do not link it)
+        assert os.path.join("math_b200", "lib", "libstanmath_cuda.so") in ldd, ldd
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900, env=env)
     tail = "\n".join(r.stdout.splitlines()[-40:])
     assert r.returncode == 0, tail
     assert "PASSED" in r.stdout, tail

@@ -1,0 +1,60 @@
+"""CPU tests of the C++ HOST LAYER against a test double of the device library.
+
+The product library has no CPU path, so without a GPU nothing behind the C ABI can run.  The host layer in front
+of it can: the include-path overlay and its routing, argument marshalling, the mapping of ABI return codes onto
+the reference's exceptions, the tape node built from the returned partials, map_rect's shard scopes.  These tests
+run the SAME gtest binaries as tests/test_cxx_gpu.py (the reference's own unit tests compiled against the overlay,
+plus test/unit/math/cuda) with tests/mock_device/mock_stan_cuda.c in front of them on LD_LIBRARY_PATH: that
+library forwards the C ABI to the plain-C oracle.  It is test infrastructure (see its header); the GPU tests run
+the binaries against the real library, found through their RUNPATH."""
+import os
+import subprocess
+
+import pytest
+
+from tests.test_cxx_gpu import BINARIES, CXX_DIR, ROOT
+
+MOCK_DIR = os.path.join(ROOT, "build", "mock")
+
+
+@pytest.fixture(scope="module")
+def mock_env():
+    os.makedirs(MOCK_DIR, exist_ok=True)
+    lib = os.path.join(MOCK_DIR, "libstanmath_cuda.so")
+    subprocess.run(["gcc", "-O2", "-std=gnu11", "-fPIC", "-shared", "-Wall", "-Wl,-soname,libstanmath_cuda.so", "-o", lib,
+                    os.path.join(ROOT, "tests", "mock_device", "mock_stan_cuda.c"),
+                    os.path.join(ROOT, "oracle", "glm_oracle.c"), "-lm"], check=True)
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = MOCK_DIR + os.pathsep + os.path.join(ROOT, "oracle", "_ref", "tbb")
+    return env
+
+
+def test_mock_exports_what_the_binaries_import(mock_env):
+    """every stan_cuda_* symbol a C++ test binary imports is one the ABI header declares and the mock defines"""
+    built = [os.path.join(CXX_DIR, b) for b in BINARIES if os.path.exists(os.path.join(CXX_DIR, b))]
+    if not built:
+        pytest.skip("C++ test binaries not built (test/Makefile needs /root/reference)")
+    wanted = set()
+    for exe in built:
+        out = subprocess.run(["nm", "-D", "--undefined-only", exe], stdout=subprocess.PIPE, text=True).stdout
+        wanted |= {line.split()[-1] for line in out.splitlines() if "stan_cuda_" in line}
+    out = subprocess.run(["nm", "-D", "--defined-only", os.path.join(MOCK_DIR, "libstanmath_cuda.so")],
+                         stdout=subprocess.PIPE, text=True).stdout
+    have = {line.split()[-1] for line in out.splitlines() if "stan_cuda_" in line}
+    header = open(os.path.join(ROOT, "include", "stan_cuda.h")).read()
+    assert wanted and wanted <= have, wanted - have
+    assert all(name + "(" in header for name in wanted)
+
+
+@pytest.mark.parametrize("name", BINARIES)
+def test_cxx_binary_against_mock_device(mock_env, name):
+    exe = os.path.join(CXX_DIR, name)
+    if not os.path.exists(exe):
+        pytest.skip("%s not built (test/Makefile needs /root/reference)" % name)
+    ldd = subprocess.run(["ldd", exe], stdout=subprocess.PIPE, text=True, env=mock_env).stdout
+    if "libstanmath_cuda.so" in ldd:   # (tests whose argument kinds never route to the device do not link it)
+        assert os.path.join("build", "mock", "libstanmath_cuda.so") in ldd, ldd
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900, env=mock_env)
+    tail = "\n".join(r.stdout.splitlines()[-40:])
+    assert r.returncode == 0, tail
+    assert "PASSED" in r.stdout and "FAILED" not in r.stdout, tail
