@@ -1,0 +1,113 @@
+#ifndef STAN_MATH_CUDA_ARENA_PARTIALS_HPP
+#define STAN_MATH_CUDA_ARENA_PARTIALS_HPP
+#ifdef STAN_CUDA
+
+#include <stan/math/cuda/marshal.hpp>
+#include <stan/math/rev/core/precomputed_gradients.hpp>
+#ifdef STAN_THREADS
+#include <tbb/blocked_range.h>
+#include <tbb/parallel_for.h>
+#endif
+#include <vector>
+
+namespace stan {
+namespace math {
+namespace cuda {
+
+/** How many reverse-mode operands an argument contributes: 0 for arithmetic arguments, 1 for a var,
+ * size() for a container of vars (the edge sizes of rev/scal/meta/operands_and_partials.hpp:72-127 and
+ * rev/mat/meta/operands_and_partials.hpp:15-73). */
+template <typename T>
+struct operand_edge {
+  static size_t size(const T& /*v*/) { return 0; }
+  static void dump(const T& /*v*/, vari** /*dst*/) {}
+};
+template <>
+struct operand_edge<var> {
+  static size_t size(const var& /*v*/) { return 1; }
+  static void dump(const var& v, vari** dst) { dst[0] = v.vi_; }
+};
+inline void dump_var_array(const var* v, size_t n, vari** dst) {
+#ifdef STAN_THREADS
+  if (n >= (size_t(1) << 16)) {
+    tbb::parallel_for(tbb::blocked_range<size_t>(0, n, size_t(1) << 15), [&](const tbb::blocked_range<size_t>& r) {
+      for (size_t i = r.begin(); i != r.end(); ++i) {
+        dst[i] = v[i].vi_;
+      }
+    });
+    return;
+  }
+#endif
+  for (size_t i = 0; i < n; ++i) {
+    dst[i] = v[i].vi_;
+  }
+}
+template <>
+struct operand_edge<std::vector<var>> {
+  static size_t size(const std::vector<var>& v) { return v.size(); }
+  static void dump(const std::vector<var>& v, vari** dst) { dump_var_array(v.data(), v.size(), dst); }
+};
+template <int R, int C, int O, int MR, int MC>
+struct operand_edge<Eigen::Matrix<var, R, C, O, MR, MC>> {
+  typedef Eigen::Matrix<var, R, C, O, MR, MC> T;
+  static size_t size(const T& v) { return v.size(); }
+  static void dump(const T& v, vari** dst) { dump_var_array(v.data(), v.size(), dst); }
+};
+
+/**
+ * The tape node of an elementwise density with N-element operands, assembled where it will live.
+ *
+ * operands_and_partials keeps the partials of a container edge in a zero-initialised Eigen vector of its own
+ * (rev/mat/meta/operands_and_partials.hpp:21-27) and build() then copies operands and partials into two arena
+ * arrays (rev/scal/meta/operands_and_partials.hpp:106-126): at N = 1e6 that is an 8 MB allocation that
+ * page-faults on every evaluation plus two 8 MB copies, a third of the host time of C1.  Here the two arena
+ * arrays are allocated first -- same allocator, same layout: edge 1, edge 2, edge 3 -- the device results are
+ * written straight into the partials array, and the node is the reference's own precomputed_gradients_vari
+ * (rev/core/precomputed_gradients.hpp:20-76, its (value, size, varis, gradients) constructor).  The arena keeps
+ * its blocks across recover_memory(), so after the first evaluation nothing is allocated from the system.
+ * A scalar operand has ONE slot that receives the sum over n, which is what broadcast_array accumulates.
+ */
+template <typename T1, typename T2 = double, typename T3 = double>
+class arena_partials {
+ public:
+  explicit arena_partials(const T1& o1, const T2& o2 = T2(), const T3& o3 = T3()) {
+    n_[0] = operand_edge<T1>::size(o1);
+    n_[1] = operand_edge<T2>::size(o2);
+    n_[2] = operand_edge<T3>::size(o3);
+    const size_t total = n_[0] + n_[1] + n_[2];
+    varis_ = nullptr;
+    partials_ = nullptr;
+    if (total > 0) {
+      varis_ = ChainableStack::instance_->memalloc_.alloc_array<vari*>(total);
+      partials_ = ChainableStack::instance_->memalloc_.alloc_array<double>(total);
+      operand_edge<T1>::dump(o1, varis_);
+      operand_edge<T2>::dump(o2, varis_ + n_[0]);
+      operand_edge<T3>::dump(o3, varis_ + n_[0] + n_[1]);
+    }
+  }
+  /** where the device writes the partials of edge e (0-based); nullptr for an arithmetic operand */
+  double* partials(int e) const {
+    if (n_[e] == 0) {
+      return nullptr;
+    }
+    return partials_ + (e > 0 ? n_[0] : 0) + (e > 1 ? n_[1] : 0);
+  }
+  return_type_t<T1, T2, T3> build(double value) const {
+    return build(value, std::integral_constant<bool, is_constant_all<T1, T2, T3>::value>());
+  }
+
+ private:
+  double build(double value, std::true_type /*all arithmetic*/) const { return value; }
+  var build(double value, std::false_type) const {
+    return var(new precomputed_gradients_vari(value, n_[0] + n_[1] + n_[2], varis_, partials_));
+  }
+  size_t n_[3];
+  vari** varis_;
+  double* partials_;
+};
+
+}  // namespace cuda
+}  // namespace math
+}  // namespace stan
+#endif
+#endif

@@ -41,7 +41,7 @@ inline const int* int_outcome_ptr(const Eigen::Matrix<int, R, C, O, MR, MC>& n) 
 /** Fills the argument block shared by the two densities and calls the C ABI. */
 template <typename T_n, typename T_prob>
 inline int int_density_call(int density, bool lp_const, const T_n& n, const T_prob& theta, size_t N,
-                            operands_and_partials<T_prob>& ops_partials, double* logp) {
+                            arena_partials<T_prob>& ops_partials, double* logp) {
   const size_t bt = staged_operand<T_prob>::bytes(theta);
   double* stage = nullptr;
   if (bt > 0) {
@@ -64,7 +64,7 @@ inline int int_density_call(int density, bool lp_const, const T_n& n, const T_pr
   }
   if (!is_constant_all<T_prob>::value) {
     a.flags |= STAN_CUDA_NEED_DALPHA;
-    a.dtheta = partials_data(ops_partials.edge1_);
+    a.dtheta = ops_partials.partials(0);
   }
   return stan_cuda_density_eval(&a);
 }
@@ -89,7 +89,7 @@ return_type_t<T_prob> bernoulli_logit_lpmf_device(const T_n& n, const T_prob& th
     check_consistent_sizes(function, "Random variable", n, "Probability parameter", theta);
     return 0.0;
   }
-  operands_and_partials<T_prob> ops_partials(theta);
+  arena_partials<T_prob> ops_partials(theta);
   double logp = 0;
   const int rc = int_density_call(STAN_CUDA_DENSITY_BERNOULLI_LOGIT, false, n, theta, N, ops_partials, &logp);
   check_cuda_rc(function, rc);
@@ -120,7 +120,7 @@ return_type_t<T_log_rate> poisson_log_lpmf_device(const T_n& n, const T_log_rate
     check_consistent_sizes(function, "Random variable", n, "Log rate parameter", alpha);
     return 0.0;
   }
-  operands_and_partials<T_log_rate> ops_partials(alpha);
+  arena_partials<T_log_rate> ops_partials(alpha);
   double logp = 0;
   const int rc = int_density_call(STAN_CUDA_DENSITY_POISSON_LOG, include_summand<propto>::value, n, alpha, N,
                                   ops_partials, &logp);

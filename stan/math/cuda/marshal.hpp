@@ -76,6 +76,26 @@ struct normal_glm_eligible
                                        && is_param_arg<T_alpha>::value && is_param_arg<T_beta>::value
                                        && is_param_arg<T_scale>::value> {};
 
+// ---- element access without a copy ----------------------------------------------------------------
+/**
+ * i-th scalar of a scalar / std::vector / Eigen vector argument, by reference.  The reference's
+ * scalar_seq_view holds the container BY VALUE (prim/scal/meta/scalar_seq_view.hpp:36: `C c_;`), i.e. it copies
+ * an N-element var vector (8 MB at N = 1e6, plus the page faults of a fresh allocation) before the first element
+ * is read; the device path reads each element exactly once, so it indexes the caller's container directly.
+ */
+template <typename T>
+struct seq_access {
+  static const T& at(const T& v, size_t /*i*/) { return v; }
+};
+template <typename S>
+struct seq_access<std::vector<S>> {
+  static const S& at(const std::vector<S>& v, size_t i) { return v[i]; }
+};
+template <typename S, int R, int C, int O, int MR, int MC>
+struct seq_access<Eigen::Matrix<S, R, C, O, MR, MC>> {
+  static const S& at(const Eigen::Matrix<S, R, C, O, MR, MC>& v, size_t i) { return v.data()[i]; }
+};
+
 // ---- values of an argument as contiguous doubles ------------------------------------------------
 /**
  * View of the values of a scalar / std::vector / Eigen vector argument as `size()` contiguous
@@ -86,9 +106,8 @@ template <typename T>
 class values {
  public:
   explicit values(const T& v) : owned_(length(v)) {
-    scalar_seq_view<T> view(v);
     for (size_t i = 0; i < owned_.size(); ++i) {
-      owned_[i] = value_of_rec(view[i]);
+      owned_[i] = value_of_rec(seq_access<T>::at(v, i));
     }
     ptr_ = owned_.data();
     size_ = owned_.size();

@@ -5,6 +5,7 @@
 #include <stan/math/cuda/c_api.h>
 #include <stan/math/cuda/err.hpp>
 #include <stan/math/cuda/marshal.hpp>
+#include <stan/math/cuda/arena_partials.hpp>
 #include <stan/math/prim/scal/err/check_consistent_sizes.hpp>
 #include <stan/math/prim/scal/err/check_finite.hpp>
 #include <stan/math/prim/scal/err/check_not_nan.hpp>
@@ -31,30 +32,29 @@ struct normal_lpdf_eligible
 
 /**
  * Values of one operand as contiguous doubles for the device.  Double containers are borrowed;
- * var / int containers are gathered -- one pass, in parallel over TBB workers when STAN_THREADS is
- * on -- straight into the thread's page-locked staging area (stan_cuda_host_staging), so the
- * upload is a DMA without a bounce buffer.  No domain checks here: the kernel tests every element.
+ * var / int containers are gathered -- one pass over the caller's container (seq_access: no scalar_seq_view
+ * copy), in parallel over TBB workers when STAN_THREADS is on -- straight into the thread's page-locked staging
+ * area (stan_cuda_host_staging), so the upload is a DMA without a bounce buffer.  No domain checks here: the kernel tests every element.
  */
 template <typename T>
 struct staged_operand {
   static constexpr bool borrowed = false;
   static size_t bytes(const T& v) { return ((length(v) + 1) & ~size_t(1)) * sizeof(double); }
   static const double* fill(const T& v, double* dst) {
-    scalar_seq_view<T> view(v);
     const size_t n = length(v);
 #ifdef STAN_THREADS
     if (n >= (size_t(1) << 16)) {
       tbb::parallel_for(tbb::blocked_range<size_t>(0, n, size_t(1) << 15),
                         [&](const tbb::blocked_range<size_t>& r) {
                           for (size_t i = r.begin(); i != r.end(); ++i) {
-                            dst[i] = value_of_rec(view[i]);
+                            dst[i] = value_of_rec(seq_access<T>::at(v, i));
                           }
                         });
       return dst;
     }
 #endif
     for (size_t i = 0; i < n; ++i) {
-      dst[i] = value_of_rec(view[i]);
+      dst[i] = value_of_rec(seq_access<T>::at(v, i));
     }
     return dst;
   }
@@ -104,7 +104,7 @@ return_type_t<T_y, T_loc, T_scale> normal_lpdf_device(const T_y& y, const T_loc&
     check_consistent_sizes(function, "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
   }
 
-  operands_and_partials<T_y, T_loc, T_scale> ops_partials(y, mu, sigma);
+  arena_partials<T_y, T_loc, T_scale> ops_partials(y, mu, sigma);  // operands_and_partials, built in place
   const size_t by = staged_operand<T_y>::bytes(y), bm = staged_operand<T_loc>::bytes(mu),
                bs = staged_operand<T_scale>::bytes(sigma);
   double* stage = nullptr;
@@ -134,15 +134,15 @@ return_type_t<T_y, T_loc, T_scale> normal_lpdf_device(const T_y& y, const T_loc&
   }
   if (!is_constant_all<T_y>::value) {
     a.flags |= STAN_CUDA_NEED_DY;
-    a.dy = partials_data(ops_partials.edge1_);
+    a.dy = ops_partials.partials(0);
   }
   if (!is_constant_all<T_loc>::value) {
     a.flags |= STAN_CUDA_NEED_DALPHA;
-    a.dmu = partials_data(ops_partials.edge2_);
+    a.dmu = ops_partials.partials(1);
   }
   if (!is_constant_all<T_scale>::value) {
     a.flags |= STAN_CUDA_NEED_DSIGMA;
-    a.dsigma = partials_data(ops_partials.edge3_);
+    a.dsigma = ops_partials.partials(2);
   }
   const int rc = stan_cuda_normal_lpdf_eval(&a);
   check_cuda_rc(function, rc);

@@ -19,6 +19,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include "../../include/stan_cuda.h"
 
@@ -29,6 +30,30 @@ int oracle_density_eval(const stan_cuda_density_args* a);
 static __thread char tl_error[256];
 static __thread int tl_scope_active, tl_scope_call, tl_scope_job, tl_scope_device;
 static unsigned long long g_evals, g_scoped_evals, g_invalidations;
+
+/* STAN_CUDA_MOCK_TIMING=1: every 10th evaluation prints the cumulative wall time spent INSIDE the three eval entry
+ * points, so that a bench binary run against the mock shows the host layer's own cost per evaluation (its total
+ * minus this).  (Not at exit: bench/stan_bench.cpp leaves through _Exit.) */
+static unsigned long long g_eval_ns;
+static int g_timing = -1;
+static double now_ns(void) {
+  struct timespec t;
+  clock_gettime(CLOCK_MONOTONIC, &t);
+  return 1e9 * (double)t.tv_sec + (double)t.tv_nsec;
+}
+static void timed_done(double t0) {
+  const unsigned long long ns = __atomic_add_fetch(&g_eval_ns, (unsigned long long)(now_ns() - t0), __ATOMIC_RELAXED);
+  if (g_timing < 0) {
+    const char* v = getenv("STAN_CUDA_MOCK_TIMING");
+    g_timing = v && *v == '1';
+  }
+  if (g_timing && g_evals % 10 == 0)
+    fprintf(stderr, "mock device: %llu evals, %.3f ms inside the eval entry points\n", g_evals, (double)ns * 1e-6);
+}
+#define TIMED(call)           \
+  const double t0_ = now_ns(); \
+  const int rc = (call);      \
+  timed_done(t0_)
 
 static int fail(int rc, const char* what) {
   snprintf(tl_error, sizeof tl_error, "mock device: %s", what);
@@ -74,7 +99,7 @@ int stan_cuda_glm_eval(const stan_cuda_glm_args* a) {
   if (outcome_out_of_range(a)) return STAN_CUDA_BAD_OUTCOME;
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
   if (tl_scope_active) __atomic_fetch_add(&g_scoped_evals, 1, __ATOMIC_RELAXED);
-  const int rc = oracle_glm_eval(a);
+  TIMED(oracle_glm_eval(a));
   return rc < 0 ? fail(rc, "stan_cuda_glm_eval: bad argument") : rc;
 }
 
@@ -85,14 +110,14 @@ int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) {
   for (int64_t i = 0; i < a->mu_len; ++i) if (!isfinite(a->mu[i])) return STAN_CUDA_BAD_OPERAND;
   for (int64_t i = 0; i < a->sigma_len; ++i) if (!(a->sigma[i] > 0.0)) return STAN_CUDA_BAD_OPERAND;
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
-  const int rc = oracle_normal_lpdf_eval(a);
+  TIMED(oracle_normal_lpdf_eval(a));
   return rc < 0 ? fail(rc, "stan_cuda_normal_lpdf_eval: bad argument") : rc;
 }
 
 int stan_cuda_density_eval(const stan_cuda_density_args* a) {
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: null args");
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
-  const int rc = oracle_density_eval(a);
+  TIMED(oracle_density_eval(a));
   return rc < 0 ? fail(rc, "stan_cuda_density_eval: bad argument") : rc;
 }
 

@@ -58,3 +58,20 @@ def test_cxx_binary_against_mock_device(mock_env, name):
     tail = "\n".join(r.stdout.splitlines()[-40:])
     assert r.returncode == 0, tail
     assert "PASSED" in r.stdout and "FAILED" not in r.stdout, tail
+
+
+def test_arena_node_equals_operands_and_partials(mock_env):
+    """bench/host_phases.cpp evaluates normal_lpdf with a var vector both ways -- the reference's operands_and_partials
+    edges + build(), and the in-place arena node of stan/math/cuda/arena_partials.hpp -- and prints the largest
+    difference over the value and all N + 1 adjoints: the two tape nodes must be identical (N above and below the
+    threshold of the parallel gather)."""
+    import json
+    exe = os.path.join(CXX_DIR, "host_phases")
+    if not os.path.exists(exe):
+        pytest.skip("host_phases not built (test/Makefile needs /root/reference)")
+    for n in ("1000", "70001"):
+        r = subprocess.run([exe, n, "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300, env=mock_env)
+        assert r.returncode == 0, r.stdout
+        out = json.loads(r.stdout)
+        assert out["max_abs_difference_of_results"] == 0.0, r.stdout
+        assert "mock device" in out["device"]
