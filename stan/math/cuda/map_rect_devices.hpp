@@ -72,7 +72,7 @@ map_rect_on_devices(const Eigen::Matrix<T_shared_param, Eigen::Dynamic, 1>& shar
     outputs_per_job[i] = static_cast<int>(per_job[i].cols());
     total_outputs += outputs_per_job[i];
   }
-  matrix_d gathered(per_job[0].rows(), total_outputs);
+  matrix_d gathered(num_jobs > 0 ? per_job[0].rows() : 0, total_outputs);  // (map_rect.hpp:164-166 returns before 0 jobs)
   int col = 0;
   for (std::size_t i = 0; i < num_jobs; ++i) {
     if (outputs_per_job[i] > 0) {

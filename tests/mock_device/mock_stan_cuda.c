@@ -60,6 +60,28 @@ static int fail(int rc, const char* what) {
   return rc;
 }
 
+/* mock-only introspection (found with dlsym by test/unit/math/cuda/map_rect_dispatch_mock_test.cpp; the product
+ * library has no such symbol): the (call_id, job, device) of every evaluation that ran inside a shard scope */
+#define MOCK_LOG_CAP 4096
+static int g_log[MOCK_LOG_CAP][3];
+static unsigned g_log_n;
+static void log_scope(void) {
+  if (!tl_scope_active) return;
+  const unsigned i = __atomic_fetch_add(&g_log_n, 1u, __ATOMIC_RELAXED);
+  if (i < MOCK_LOG_CAP) {
+    g_log[i][0] = tl_scope_call;
+    g_log[i][1] = tl_scope_job;
+    g_log[i][2] = tl_scope_device;
+  }
+}
+int stan_cuda_mock_scope_log(int* out, int cap) { /* out[3 * i + {0,1,2}]; returns the number of entries; resets the log */
+  const unsigned n = g_log_n < MOCK_LOG_CAP ? g_log_n : MOCK_LOG_CAP;
+  for (unsigned i = 0; i < n && (int)i < cap; ++i) memcpy(out + 3 * i, g_log[i], sizeof g_log[i]);
+  g_log_n = 0;
+  return (int)n;
+}
+int stan_cuda_mock_scope_active(void) { return tl_scope_active; }
+
 int stan_cuda_init(int n_devices) { (void)n_devices; return STAN_CUDA_OK; }
 int stan_cuda_device_count(void) {
   const char* v = getenv("STAN_CUDA_MOCK_DEVICES");   /* lets a test see map_rect's job -> device dispatch */
@@ -93,12 +115,32 @@ static int outcome_out_of_range(const stan_cuda_glm_args* a) {
   return 0;
 }
 
+/* STAN_CUDA_MOCK_NO_COMPUTE=1 (timing of the host layer alone, bench binaries only): the GLM entry point returns at
+ * once with zeroed outputs, so that what a bench binary measures is the C++ layer in front of the ABI */
+static int no_compute(void) {
+  static int on = -1;
+  if (on < 0) {
+    const char* v = getenv("STAN_CUDA_MOCK_NO_COMPUTE");
+    on = v && *v == '1';
+  }
+  return on;
+}
+
 int stan_cuda_glm_eval(const stan_cuda_glm_args* a) {
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null args");
+  if (no_compute()) {
+    if (a->lp) *a->lp = -1.0;
+    if (a->dbeta) memset(a->dbeta, 0, (size_t)(a->k * (a->n_classes > 0 ? a->n_classes : 1)) * sizeof(double));
+    if (a->dalpha && a->alpha_len == 1) a->dalpha[0] = 0.0;
+    if (a->dsigma && a->sigma_len == 1) a->dsigma[0] = 0.0;
+    if (a->aux) memset(a->aux, 0, 4 * sizeof(double));
+    return STAN_CUDA_OK;
+  }
   if (a->n > 0 && (!a->y || (!a->x && a->k > 0))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null x or y");
   if (outcome_out_of_range(a)) return STAN_CUDA_BAD_OUTCOME;
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
   if (tl_scope_active) __atomic_fetch_add(&g_scoped_evals, 1, __ATOMIC_RELAXED);
+  log_scope();
   TIMED(oracle_glm_eval(a));
   return rc < 0 ? fail(rc, "stan_cuda_glm_eval: bad argument") : rc;
 }

@@ -75,3 +75,15 @@ def test_arena_node_equals_operands_and_partials(mock_env):
         out = json.loads(r.stdout)
         assert out["max_abs_difference_of_results"] == 0.0, r.stdout
         assert "mock device" in out["device"]
+
+
+def test_map_rect_dispatch_against_mock_device(mock_env):
+    """test/unit/math/cuda/map_rect_dispatch_mock_test.cpp: job i of a map_rect call evaluates inside the shard scope
+    (call_id, i, i mod G); the scope is closed when a job throws; evaluations outside map_rect carry no scope.  The
+    mock reports 3 devices and records the scope of every evaluation."""
+    exe = os.path.join(CXX_DIR, "cuda_map_rect_dispatch_mock_test")
+    if not os.path.exists(exe):
+        pytest.skip("not built (test/Makefile needs /root/reference)")
+    env = dict(mock_env, STAN_CUDA_MOCK_DEVICES="3", STAN_NUM_THREADS="4")
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and "PASSED  ] 2 tests" in r.stdout, r.stdout[-3000:]
