@@ -96,12 +96,13 @@ struct Scope {
 };
 static thread_local Scope tl_scope;
 
-static uint64_t fnv(uint64_t h, uint64_t v) {
-  for (int i = 0; i < 8; ++i) {
-    h ^= (v >> (8 * i)) & 0xff;
-    h *= 1099511628211ull;
-  }
-  return h;
+// One multiply per sampled word (a byte-wise FNV has a dependent chain of 8 multiplies per word, which made the
+// hashing -- not the 128 scattered loads -- the cost of a fingerprint: 2.0 us warm / 18 us cold per evaluation at
+// C2 on the dev container's CPU, 0.4 / 7.5 us with this mix: the short chain also lets the loads overlap).
+static inline uint64_t fnv(uint64_t h, uint64_t v) {
+  h ^= v;
+  h *= 0x9E3779B97F4A7C15ull;
+  return h ^ (h >> 29);
 }
 
 // Content fingerprint from <= 64 sampled elements of each array: catches an address that is
