@@ -4,10 +4,6 @@
 
 #include <stan/math/cuda/marshal.hpp>
 #include <stan/math/rev/core/precomputed_gradients.hpp>
-#ifdef STAN_THREADS
-#include <tbb/blocked_range.h>
-#include <tbb/parallel_for.h>
-#endif
 #include <vector>
 
 namespace stan {
@@ -28,19 +24,11 @@ struct operand_edge<var> {
   static void dump(const var& v, vari** dst) { dst[0] = v.vi_; }
 };
 inline void dump_var_array(const var* v, size_t n, vari** dst) {
-#ifdef STAN_THREADS
-  if (n >= (size_t(1) << 16)) {
-    tbb::parallel_for(tbb::blocked_range<size_t>(0, n, size_t(1) << 15), [&](const tbb::blocked_range<size_t>& r) {
-      for (size_t i = r.begin(); i != r.end(); ++i) {
-        dst[i] = v[i].vi_;
-      }
-    });
-    return;
-  }
-#endif
-  for (size_t i = 0; i < n; ++i) {
-    dst[i] = v[i].vi_;
-  }
+  for_each_chunk(n, [&](size_t begin, size_t end) {
+    for (size_t i = begin; i != end; ++i) {
+      dst[i] = v[i].vi_;
+    }
+  });
 }
 template <>
 struct operand_edge<std::vector<var>> {

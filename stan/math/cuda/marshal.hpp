@@ -10,12 +10,41 @@
 #include <stan/math/prim/scal/fun/value_of_rec.hpp>
 #include <stan/math/rev/core.hpp>
 #include <stan/math/rev/meta.hpp>
+#ifdef STAN_THREADS
+#include <tbb/blocked_range.h>
+#include <tbb/parallel_for.h>
+#include <tbb/task_arena.h>
+#endif
 #include <type_traits>
 #include <vector>
 
 namespace stan {
 namespace math {
 namespace cuda {
+
+/**
+ * body(begin, end) over [0, n): in parallel over the TBB workers for the N-element operand passes of the
+ * elementwise densities, serially below 65536 elements or without STAN_THREADS.
+ *
+ * The parallel loop runs ISOLATED (tbb::this_task_arena::isolate).  These passes are nested parallelism whenever the
+ * density is evaluated inside a map_rect job: a worker that waits in a plain nested parallel_for may be handed
+ * ANOTHER map_rect job, which would evaluate on the same thread -- overwriting this thread's staging buffer
+ * (stan_cuda_host_staging is per thread) and leaving the shard scope of the outer job closed.  Isolation restricts
+ * the waiting thread to tasks of this loop (test: map_rect_dispatch_mock_test.cpp, nested_parallel_gather_...).
+ */
+template <typename Body>
+inline void for_each_chunk(size_t n, const Body& body) {
+#ifdef STAN_THREADS
+  if (n >= (size_t(1) << 16)) {
+    tbb::this_task_arena::isolate([&] {
+      tbb::parallel_for(tbb::blocked_range<size_t>(0, n, size_t(1) << 15),
+                        [&](const tbb::blocked_range<size_t>& r) { body(r.begin(), r.end()); });
+    });
+    return;
+  }
+#endif
+  body(size_t(0), n);
+}
 
 // ---- which instantiations take the GPU path ---------------------------------------
 template <typename T>

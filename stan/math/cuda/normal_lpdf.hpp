@@ -11,10 +11,6 @@
 #include <stan/math/prim/scal/err/check_not_nan.hpp>
 #include <stan/math/prim/scal/err/check_positive.hpp>
 #include <stan/math/prim/scal/fun/size_zero.hpp>
-#ifdef STAN_THREADS
-#include <tbb/blocked_range.h>
-#include <tbb/parallel_for.h>
-#endif
 #include <stdexcept>
 #include <string>
 
@@ -41,21 +37,11 @@ struct staged_operand {
   static constexpr bool borrowed = false;
   static size_t bytes(const T& v) { return ((length(v) + 1) & ~size_t(1)) * sizeof(double); }
   static const double* fill(const T& v, double* dst) {
-    const size_t n = length(v);
-#ifdef STAN_THREADS
-    if (n >= (size_t(1) << 16)) {
-      tbb::parallel_for(tbb::blocked_range<size_t>(0, n, size_t(1) << 15),
-                        [&](const tbb::blocked_range<size_t>& r) {
-                          for (size_t i = r.begin(); i != r.end(); ++i) {
-                            dst[i] = value_of_rec(seq_access<T>::at(v, i));
-                          }
-                        });
-      return dst;
-    }
-#endif
-    for (size_t i = 0; i < n; ++i) {
-      dst[i] = value_of_rec(seq_access<T>::at(v, i));
-    }
+    for_each_chunk(length(v), [&](size_t begin, size_t end) {
+      for (size_t i = begin; i != end; ++i) {
+        dst[i] = value_of_rec(seq_access<T>::at(v, i));
+      }
+    });
     return dst;
   }
 };

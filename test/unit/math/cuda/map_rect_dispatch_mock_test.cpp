@@ -103,3 +103,53 @@ TEST(CudaMapRectDispatch, scope_is_left_when_a_job_throws_and_outside_map_rect) 
   EXPECT_EQ(0, log(scratch.data(), 4096));
   stan::math::recover_memory();
 }
+
+// A job whose functor evaluates a vectorised normal_lpdf large enough for the parallel operand gather
+// (stan/math/cuda/normal_lpdf.hpp: N >= 65536).  The gather is a nested tbb::parallel_for: while a worker waits in
+// it, TBB may hand it ANOTHER map_rect job, whose evaluation uses the same thread-local staging buffer.  The gathers
+// therefore run isolated (tbb::this_task_arena::isolate); this test fails without the isolation.
+struct shard_normal {
+  template <typename T1, typename T2>
+  Matrix<typename stan::return_type<T1, T2>::type, Dynamic, 1> operator()(const Matrix<T1, Dynamic, 1>& shared,
+                                                                         const Matrix<T2, Dynamic, 1>& job,
+                                                                         const std::vector<double>& x_r,
+                                                                         const std::vector<int>& x_i,
+                                                                         std::ostream* msgs = 0) const {
+    typedef typename stan::return_type<T1, T2>::type T;
+    const int n = x_i[0];
+    Matrix<T, Dynamic, 1> mu(n), sg(n);
+    for (int i = 0; i < n; ++i) {
+      mu[i] = shared[0] + job[0] * x_r[i];
+      sg[i] = shared[1] + 0.001 * (i % 7);
+    }
+    std::vector<double> y(x_r.begin(), x_r.end());
+    Matrix<T, Dynamic, 1> res(1);
+    res(0) = stan::math::normal_lpdf(y, mu, sg);
+    return res;
+  }
+};
+
+TEST(CudaMapRectDispatch, nested_parallel_gather_does_not_mix_jobs) {
+  const int J = 24, n = 70000;
+  std::vector<std::vector<double>> x_r(J, std::vector<double>(n));
+  std::vector<std::vector<int>> x_i(J, std::vector<int>(1, n));
+  for (int j = 0; j < J; ++j)
+    for (int i = 0; i < n; ++i) x_r[j][i] = std::sin(0.01 * i + j);
+  for (int rep = 0; rep < 3; ++rep) {
+    Matrix<var, Dynamic, 1> shared(2);
+    shared << 0.1, 1.2;
+    std::vector<Matrix<var, Dynamic, 1>> job(J, Matrix<var, Dynamic, 1>(1));
+    for (int j = 0; j < J; ++j) job[j][0] = 0.5 + 0.1 * j;
+    Matrix<var, Dynamic, 1> out = stan::math::map_rect<43, shard_normal>(shared, job, x_r, x_i);
+    for (int j = 0; j < J; ++j) {
+      double ref = 0;  // normal_lpdf.hpp:89-97 by hand
+      for (int i = 0; i < n; ++i) {
+        const double mu = 0.1 + (0.5 + 0.1 * j) * x_r[j][i], sg = 1.2 + 0.001 * (i % 7);
+        const double z = (x_r[j][i] - mu) / sg;
+        ref += -0.91893853320467274178 - std::log(sg) - 0.5 * z * z;
+      }
+      EXPECT_NEAR(ref, out[j].val(), 1e-9 * std::fabs(ref)) << "job " << j << " rep " << rep;
+    }
+    stan::math::recover_memory();
+  }
+}
