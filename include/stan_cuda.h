@@ -257,7 +257,8 @@ STAN_CUDA_API void stan_cuda_cache_set_limit(int64_t bytes);
 /* Inside a scope, evaluations of the calling thread run on `device` and their data is keyed by
  * (call_id, job) instead of by host pointer: the functor rebuilds X from x_r on every call, so
  * its address is not an identity; the immutability contract is map_rect's own
- * (stan/math/prim/mat/functor/map_rect.hpp:97-100). */
+ * (stan/math/prim/mat/functor/map_rect.hpp:97-100).  Scopes nest (up to 8 deep): exit restores the scope that was
+ * current at the matching enter. */
 STAN_CUDA_API void stan_cuda_shard_scope_enter(int call_id, int job, int device);
 STAN_CUDA_API void stan_cuda_shard_scope_exit(void);
 

@@ -923,13 +923,24 @@ int64_t stan_cuda_cache_bytes(void) {
   return b;
 }
 
+// Scopes nest: exit restores the scope that was current at the matching enter (a job whose functor runs nested
+// TBB parallelism of its own can be handed another job of the same map_rect call while it waits).
+static thread_local Scope tl_scope_saved[8];
+static thread_local int tl_scope_depth = 0;
+
 void stan_cuda_shard_scope_enter(int call_id, int job, int device) {
+  if (tl_scope_depth < 8) tl_scope_saved[tl_scope_depth] = tl_scope;
+  ++tl_scope_depth;
   tl_scope.active = true;
   tl_scope.call_id = call_id;
   tl_scope.job = job;
   tl_scope.device = device < 0 ? 0 : device;
 }
 
-void stan_cuda_shard_scope_exit(void) { tl_scope.active = false; }
+void stan_cuda_shard_scope_exit(void) {
+  if (tl_scope_depth > 0) --tl_scope_depth;
+  if (tl_scope_depth < 8) tl_scope = tl_scope_saved[tl_scope_depth];
+  if (tl_scope_depth == 0) tl_scope.active = false;
+}
 
 }  // extern "C"

@@ -153,3 +153,31 @@ TEST(CudaMapRectDispatch, nested_parallel_gather_does_not_mix_jobs) {
     stan::math::recover_memory();
   }
 }
+
+TEST(CudaMapRectDispatch, scopes_nest) {
+  scope_log_fn log = mock_scope_log();
+  if (!log) return;
+  std::vector<int> scratch(3 * 4096);
+  log(scratch.data(), 4096);
+  const int rows = 10, k = 2;
+  std::vector<std::vector<double>> x_r;
+  std::vector<std::vector<int>> x_i;
+  make_jobs(1, rows, k, &x_r, &x_i);
+  MatrixXd x = Eigen::Map<const MatrixXd>(x_r[0].data(), rows, k);
+  std::vector<int> y(x_i[0].begin() + 2, x_i[0].end());
+  Eigen::VectorXd beta = Eigen::VectorXd::Constant(k, 0.1);
+  {
+    stan::math::cuda::shard_scope outer(7, 1, 1);
+    {
+      stan::math::cuda::shard_scope inner(7, 2, 2);
+      stan::math::poisson_log_glm_lpmf(y, x, 0.3, beta);
+    }
+    stan::math::poisson_log_glm_lpmf(y, x, 0.3, beta);  // back in the outer scope
+  }
+  stan::math::poisson_log_glm_lpmf(y, x, 0.3, beta);  // no scope
+  ASSERT_EQ(2, log(scratch.data(), 4096));
+  EXPECT_EQ(2, scratch[1]);
+  EXPECT_EQ(2, scratch[2]);
+  EXPECT_EQ(1, scratch[4]);
+  EXPECT_EQ(1, scratch[5]);
+}

@@ -184,10 +184,29 @@ int stan_cuda_cache_invalidate(const void* host_ptr) {
 void stan_cuda_cache_clear(void) {}
 int64_t stan_cuda_cache_bytes(void) { return 0; }
 
+/* scopes nest, as in the product (api.cu): exit restores the scope current at the matching enter */
+static __thread int tl_saved[8][4];
+static __thread int tl_depth;
 void stan_cuda_shard_scope_enter(int call_id, int job, int device) {
+  if (tl_depth < 8) {
+    tl_saved[tl_depth][0] = tl_scope_active;
+    tl_saved[tl_depth][1] = tl_scope_call;
+    tl_saved[tl_depth][2] = tl_scope_job;
+    tl_saved[tl_depth][3] = tl_scope_device;
+  }
+  ++tl_depth;
   tl_scope_active = 1;
   tl_scope_call = call_id;
   tl_scope_job = job;
   tl_scope_device = device;
 }
-void stan_cuda_shard_scope_exit(void) { tl_scope_active = 0; }
+void stan_cuda_shard_scope_exit(void) {
+  if (tl_depth > 0) --tl_depth;
+  if (tl_depth < 8) {
+    tl_scope_active = tl_saved[tl_depth][0];
+    tl_scope_call = tl_saved[tl_depth][1];
+    tl_scope_job = tl_saved[tl_depth][2];
+    tl_scope_device = tl_saved[tl_depth][3];
+  }
+  if (tl_depth == 0) tl_scope_active = 0;
+}

@@ -86,4 +86,4 @@ def test_map_rect_dispatch_against_mock_device(mock_env):
         pytest.skip("not built (test/Makefile needs /root/reference)")
     env = dict(mock_env, STAN_CUDA_MOCK_DEVICES="3", STAN_NUM_THREADS="4")
     r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300, env=env)
-    assert r.returncode == 0 and "PASSED  ] 3 tests" in r.stdout, r.stdout[-3000:]
+    assert r.returncode == 0 and "PASSED  ] 4 tests" in r.stdout, r.stdout[-3000:]
