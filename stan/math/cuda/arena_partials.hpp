@@ -55,41 +55,54 @@ struct operand_edge<Eigen::Matrix<var, R, C, O, MR, MC>> {
  * its blocks across recover_memory(), so after the first evaluation nothing is allocated from the system.
  * A scalar operand has ONE slot that receives the sum over n, which is what broadcast_array accumulates.
  */
-template <typename T1, typename T2 = double, typename T3 = double>
+template <typename T1, typename T2 = double, typename T3 = double, typename T4 = double, typename T5 = double>
 class arena_partials {
  public:
-  explicit arena_partials(const T1& o1, const T2& o2 = T2(), const T3& o3 = T3()) {
+  explicit arena_partials(const T1& o1, const T2& o2 = T2(), const T3& o3 = T3(), const T4& o4 = T4(),
+                          const T5& o5 = T5()) {
     n_[0] = operand_edge<T1>::size(o1);
     n_[1] = operand_edge<T2>::size(o2);
     n_[2] = operand_edge<T3>::size(o3);
-    const size_t total = n_[0] + n_[1] + n_[2];
+    n_[3] = operand_edge<T4>::size(o4);
+    n_[4] = operand_edge<T5>::size(o5);
+    off_[0] = 0;
+    for (int e = 1; e <= 5; ++e) {
+      off_[e] = off_[e - 1] + n_[e - 1];
+    }
     varis_ = nullptr;
     partials_ = nullptr;
-    if (total > 0) {
-      varis_ = ChainableStack::instance_->memalloc_.alloc_array<vari*>(total);
-      partials_ = ChainableStack::instance_->memalloc_.alloc_array<double>(total);
-      operand_edge<T1>::dump(o1, varis_);
-      operand_edge<T2>::dump(o2, varis_ + n_[0]);
-      operand_edge<T3>::dump(o3, varis_ + n_[0] + n_[1]);
+    if (off_[5] > 0) {
+      varis_ = ChainableStack::instance_->memalloc_.alloc_array<vari*>(off_[5]);
+      partials_ = ChainableStack::instance_->memalloc_.alloc_array<double>(off_[5]);
+      operand_edge<T1>::dump(o1, varis_ + off_[0]);
+      operand_edge<T2>::dump(o2, varis_ + off_[1]);
+      operand_edge<T3>::dump(o3, varis_ + off_[2]);
+      operand_edge<T4>::dump(o4, varis_ + off_[3]);
+      operand_edge<T5>::dump(o5, varis_ + off_[4]);
     }
   }
-  /** where the device writes the partials of edge e (0-based); nullptr for an arithmetic operand */
-  double* partials(int e) const {
-    if (n_[e] == 0) {
-      return nullptr;
+  /** where the device writes the partials of edge e (0-based, in argument order); nullptr for an arithmetic
+   * operand.  Every slot the caller asks the device for is written by it; slots of edges it does not ask for must
+   * be set by the caller (zero()). */
+  double* partials(int e) const { return n_[e] == 0 ? nullptr : partials_ + off_[e]; }
+  size_t size(int e) const { return n_[e]; }
+  /** sets the partials of edge e to zero (operands_and_partials starts from zeroed partials) */
+  void zero(int e) const {
+    for (size_t i = 0; i < n_[e]; ++i) {
+      partials_[off_[e] + i] = 0.0;
     }
-    return partials_ + (e > 0 ? n_[0] : 0) + (e > 1 ? n_[1] : 0);
   }
-  return_type_t<T1, T2, T3> build(double value) const {
-    return build(value, std::integral_constant<bool, is_constant_all<T1, T2, T3>::value>());
+  return_type_t<T1, T2, T3, T4, T5> build(double value) const {
+    return build(value, std::integral_constant<bool, is_constant_all<T1, T2, T3, T4, T5>::value>());
   }
 
  private:
   double build(double value, std::true_type /*all arithmetic*/) const { return value; }
   var build(double value, std::false_type) const {
-    return var(new precomputed_gradients_vari(value, n_[0] + n_[1] + n_[2], varis_, partials_));
+    return var(new precomputed_gradients_vari(value, off_[5], varis_, partials_));
   }
-  size_t n_[3];
+  size_t n_[5];
+  size_t off_[6];
   vari** varis_;
   double* partials_;
 };

@@ -15,6 +15,7 @@
 #include <tbb/parallel_for.h>
 #include <tbb/task_arena.h>
 #endif
+#include <memory>
 #include <type_traits>
 #include <vector>
 
@@ -134,20 +135,20 @@ struct seq_access<Eigen::Matrix<S, R, C, O, MR, MC>> {
 template <typename T>
 class values {
  public:
-  explicit values(const T& v) : owned_(length(v)) {
-    for (size_t i = 0; i < owned_.size(); ++i) {
-      owned_[i] = value_of_rec(seq_access<T>::at(v, i));
-    }
-    ptr_ = owned_.data();
-    size_ = owned_.size();
+  explicit values(const T& v) : owned_(new double[length(v) > 0 ? length(v) : 1]), size_(length(v)) {
+    double* dst = owned_.get();  // uninitialised storage: every element is written by the gather below
+    for_each_chunk(size_, [&](size_t begin, size_t end) {  // N-element intercepts / scales: in parallel
+      for (size_t i = begin; i != end; ++i) {
+        dst[i] = value_of_rec(seq_access<T>::at(v, i));
+      }
+    });
   }
-  const double* data() const { return ptr_; }
+  const double* data() const { return owned_.get(); }
   size_t size() const { return size_; }
   bool borrowed() const { return false; }
 
  private:
-  std::vector<double> owned_;
-  const double* ptr_;
+  std::unique_ptr<double[]> owned_;
   size_t size_;
 };
 

@@ -2,6 +2,7 @@
 #define STAN_MATH_CUDA_NEG_BINOMIAL_2_LOG_GLM_LPMF_HPP
 #ifdef STAN_CUDA
 
+#include <stan/math/cuda/arena_partials.hpp>
 #include <stan/math/cuda/glm_call.hpp>
 #include <stan/math/prim/scal/err/check_consistent_size.hpp>
 #include <stan/math/prim/scal/err/check_consistent_sizes.hpp>
@@ -57,7 +58,7 @@ return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(c
   values<T_precision> phi_val(phi);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_NEG_BINOMIAL_2_LOG, x, alpha, beta);
   const double x_placeholder = 0;
-  operands_and_partials<double, T_alpha, T_beta, T_precision> ops_partials(x_placeholder, alpha, beta, phi);
+  arena_partials<double, T_alpha, T_beta, T_precision> ops_partials(x_placeholder, alpha, beta, phi);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_is_double = 0;
@@ -75,15 +76,15 @@ return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(c
   }
   if (!is_constant_all<T_beta>::value) {
     a.flags |= STAN_CUDA_NEED_DBETA;
-    a.dbeta = partials_data(ops_partials.edge3_);
+    a.dbeta = ops_partials.partials(2);
   }
   if (!is_constant_all<T_alpha>::value) {
     a.flags |= STAN_CUDA_NEED_DALPHA;
-    a.dalpha = partials_data(ops_partials.edge2_);
+    a.dalpha = ops_partials.partials(1);
   }
   if (!is_constant_all<T_precision>::value) {
     a.flags |= STAN_CUDA_NEED_DSIGMA;
-    a.dsigma = partials_data(ops_partials.edge4_);
+    a.dsigma = ops_partials.partials(3);
   }
   // eager O(K) parameter checks, after the outcome check in the reference's order
   int rc = STAN_CUDA_OK;

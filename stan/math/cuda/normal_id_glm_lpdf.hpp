@@ -2,6 +2,7 @@
 #define STAN_MATH_CUDA_NORMAL_ID_GLM_LPDF_HPP
 #ifdef STAN_CUDA
 
+#include <stan/math/cuda/arena_partials.hpp>
 #include <stan/math/cuda/glm_call.hpp>
 #include <stan/math/prim/scal/err/check_consistent_size.hpp>
 #include <stan/math/prim/scal/err/check_consistent_sizes.hpp>
@@ -48,7 +49,7 @@ return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_NORMAL_ID, x, alpha, beta);
   // x is data on this path: its (empty) edge is declared on a double so that views of x work too
   const double x_placeholder = 0;
-  operands_and_partials<T_y, double, T_alpha, T_beta, T_scale> ops_partials(y, x_placeholder, alpha, beta, sigma);
+  arena_partials<T_y, double, T_alpha, T_beta, T_scale> ops_partials(y, x_placeholder, alpha, beta, sigma);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_is_double = 1;
@@ -65,20 +66,20 @@ return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y
   if (!is_constant_all<T_y>::value) {
     if (is_vector<T_y>::value) {  // per-row partials; a scalar var y gets the sum below
       a.flags |= STAN_CUDA_NEED_DY;
-      a.dy = partials_data(ops_partials.edge1_);
+      a.dy = ops_partials.partials(0);
     }
   }
   if (!is_constant_all<T_alpha>::value) {
     a.flags |= STAN_CUDA_NEED_DALPHA;
-    a.dalpha = partials_data(ops_partials.edge3_);
+    a.dalpha = ops_partials.partials(2);
   }
   if (!is_constant_all<T_beta>::value) {
     a.flags |= STAN_CUDA_NEED_DBETA;
-    a.dbeta = partials_data(ops_partials.edge4_);
+    a.dbeta = ops_partials.partials(3);
   }
   if (!is_constant_all<T_scale>::value) {
     a.flags |= STAN_CUDA_NEED_DSIGMA;
-    a.dsigma = partials_data(ops_partials.edge5_);
+    a.dsigma = ops_partials.partials(4);
   }
   if (call.run(function) == STAN_CUDA_NONFINITE) {
     const double y_scaled_sq_sum = call.witness();
@@ -88,7 +89,7 @@ return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y
     check_finite(function, "Matrix of independent variables", y_scaled_sq_sum);
   }
   if (!is_constant_all<T_y>::value && !is_vector<T_y>::value) {
-    double* dy = partials_data(ops_partials.edge1_);
+    double* dy = ops_partials.partials(0);
     if (dy) {
       *dy = -call.sum_d();  // sum of -mu_derivative over the rows the scalar is broadcast to
     }

@@ -2,6 +2,7 @@
 #define STAN_MATH_CUDA_POISSON_LOG_GLM_LPMF_HPP
 #ifdef STAN_CUDA
 
+#include <stan/math/cuda/arena_partials.hpp>
 #include <stan/math/cuda/glm_call.hpp>
 #include <stan/math/prim/scal/err/check_consistent_size.hpp>
 #include <stan/math/prim/scal/err/check_consistent_sizes.hpp>
@@ -46,7 +47,7 @@ return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_POISSON_LOG, x, alpha, beta);
   // x is data on this path: its (empty) edge is declared on a double so that views of x work too
   const double x_placeholder = 0;
-  operands_and_partials<double, T_alpha, T_beta> ops_partials(x_placeholder, alpha, beta);
+  arena_partials<double, T_alpha, T_beta> ops_partials(x_placeholder, alpha, beta);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_is_double = 0;
@@ -59,11 +60,11 @@ return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T
   }
   if (!is_constant_all<T_beta>::value) {
     a.flags |= STAN_CUDA_NEED_DBETA;
-    a.dbeta = partials_data(ops_partials.edge3_);
+    a.dbeta = ops_partials.partials(2);
   }
   if (!is_constant_all<T_alpha>::value) {
     a.flags |= STAN_CUDA_NEED_DALPHA;
-    a.dalpha = partials_data(ops_partials.edge2_);
+    a.dalpha = ops_partials.partials(1);
   }
   int rc = call.run(function);
   if (rc == STAN_CUDA_BAD_OUTCOME) {
