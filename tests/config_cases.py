@@ -68,3 +68,9 @@ def inputs_reproduce(man, name, x, y):
     """True when this host regenerated the inputs bit for bit (same torch build, same sampling code path);
     a test skips, with the reason, when it did not — the stored outputs belong to the stored inputs only."""
     return man["configs"][name]["inputs_sha256"] == input_checksum(x, y)
+
+
+def c5_inputs_reproduce(man, shards):
+    """the same for the 64 shards of C5: `shards` = [c5_shard(j) for every j], in order"""
+    sums = "".join(input_checksum(s[0], s[1]) for s in shards)
+    return man["configs"]["c5"]["inputs_sha256"] == hashlib.sha256(sums.encode()).hexdigest()

@@ -58,8 +58,10 @@ def test_c1_oracle_against_stored_reference(stored, L):
 
 @pytest.mark.parametrize("j", [0, 31, 63])
 def test_c5_shard_oracle_against_stored_reference(stored, L, j):
-    golden, _ = stored
+    golden, man = stored
     x, y, alpha, beta = cc.c5_shard(j)
+    if j == 0 and not cc.c5_inputs_reproduce(man, [cc.c5_shard(q) for q in range(cc.C5["shards"])]):
+        pytest.skip("inputs do not regenerate bit for bit on this host")
     r = L.oracle_glm(cc.C5["family"], x, y, alpha, beta)
     assert_close(r["lp"], golden["c5/lp"][j], "C5 shard lp")
     assert_close(r["dbeta"], golden["c5/dbeta"][j], "C5 shard dbeta")

@@ -54,8 +54,10 @@ def test_glm_config_against_stored_reference(glm, stored, name):
 
 def test_c5_all_shards_batched_and_single_against_stored_reference(glm, stored):
     """the 64 shards of C5: one batched launch, and shard by shard, both against the reference's per-shard outputs"""
-    golden, _ = stored
+    golden, man = stored
     shards = [cc.c5_shard(j) for j in range(cc.C5["shards"])]
+    if not cc.c5_inputs_reproduce(man, shards):
+        pytest.skip("inputs do not regenerate bit for bit on this host")
     batch = glm.GlmBatch(cc.C5["family"], [s[0] for s in shards], [s[1] for s in shards], call_id=5005)
     rc, res = batch.eval([s[2][0] for s in shards], np.stack([s[3] for s in shards]))
     assert rc == 0
