@@ -118,3 +118,28 @@ def test_cxx_routing_table_compiles_and_runs_without_a_gpu():
         pytest.skip("not built (test/Makefile needs /root/reference)")
     r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
     assert r.returncode == 0 and "PASSED" in r.stdout, r.stdout
+
+
+def test_product_never_references_the_oracle_or_the_test_double():
+    """oracle/ and tests/mock_device/ are test infrastructure: nothing the product is made of includes, links, loads or
+    names a path into them (comments that cite a test file by name are fine), and the built library neither needs nor
+    defines an oracle symbol."""
+    import re
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pat = re.compile(r"(#\s*include[^\n]*(oracle|mock_device))|(oracle/|liboracle|libstanref|mock_device|build/mock)")
+    offenders = []
+    for top in ("math_b200", "stan", "overlay", "include"):
+        for d, _, files in os.walk(os.path.join(root, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h", ".cpp")):
+                    text = open(os.path.join(d, f), errors="replace").read()
+                    if pat.search(text):
+                        offenders.append(os.path.relpath(os.path.join(d, f), root))
+    assert not offenders, offenders
+    lib = os.path.join(root, "math_b200", "lib", "libstanmath_cuda.so")
+    if os.path.exists(lib):
+        out = subprocess.run(["nm", "-D", lib], stdout=subprocess.PIPE, text=True).stdout
+        assert "oracle_" not in out and "stanref_" not in out and "stan_cuda_mock" not in out
+        needed = subprocess.run(["readelf", "-d", lib], stdout=subprocess.PIPE, text=True).stdout
+        assert "liboracle" not in needed and "libstanref" not in needed
