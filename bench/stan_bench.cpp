@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -162,6 +162,28 @@ double glm_eval_once(const Problem& p, Result* out) {
   for (int64_t j = 0; j < p.k; ++j) out->grad[j] = beta[j].adj();
   out->grad[p.k] = alpha.adj();
   out->grad[p.k + 1] = p.family == 2 ? sigma.adj() : 0.0;
+  const double t1 = now();
+  recover_memory_nested();
+  return t1 - t0;
+}
+
+// the per-row variant -- bernoulli_logit_glm_lpmf with the intercept a var VECTOR of length N
+// (varying intercepts); one evaluation = forward + grad() + reading the K + N adjoints
+template <bool GPU>
+double glm_vector_alpha_once(const Problem& p, Result* out) {
+  using namespace stan::math;  // NOLINT
+  start_nested();
+  vector_v beta(p.k), alpha(p.n);
+  for (int64_t j = 0; j < p.k; ++j) beta[j] = p.beta[j];
+  for (int64_t i = 0; i < p.n; ++i) alpha[i] = p.alpha + 0.001 * double(i % 97);
+  const double t0 = now();
+  var lp = GPU ? bernoulli_logit_glm_lpmf(p.y_int, p.x, alpha, beta)
+               : bernoulli_logit_glm_lpmf_reference_cpu<false>(p.y_int, p.x, alpha, beta);
+  grad(lp.vi_);
+  out->lp = lp.val();
+  out->grad.resize(p.k + p.n);
+  for (int64_t j = 0; j < p.k; ++j) out->grad[j] = beta[j].adj();
+  for (int64_t i = 0; i < p.n; ++i) out->grad[p.k + i] = alpha[i].adj();
   const double t1 = now();
   recover_memory_nested();
   return t1 - t0;
@@ -490,6 +512,25 @@ int run(int argc, char** argv) {
       if (!cpu_only) std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
     }
     std::printf("%s\"algorithmic_bytes\": %lld}\n", no_cpu ? "" : ", ", (long long)(J * (rows * k * 8 + rows * 4)));
+    return 0;
+  }
+
+  if (config == "v2") {  // C2 with a var intercept vector
+    const int64_t n = n_override ? n_override : 1000000, k = 32;
+    Problem p;
+    make_problem(&p, 0, n, k, 1000, threads);
+    Result g, c;
+    glm_vector_alpha_once<true>(p, &g);  // cache fill
+    Timing tg = time_reps(3, reps, 60, [&] { return glm_vector_alpha_once<true>(p, &g); });
+    std::printf("\"what\": \"bernoulli_logit_glm_lpmf N=%lld K=%lld, var beta, var intercept VECTOR\", ", (long long)n, (long long)k);
+    print_timing("gpu", tg);
+    if (!no_cpu) {
+      Timing tc = time_reps(1, std::max(cpu_reps, 3), 60, [&] { return glm_vector_alpha_once<false>(p, &c); });
+      std::printf(", ");
+      print_timing("cpu_reference_1_thread", tc);
+      std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
+    }
+    std::printf(", \"algorithmic_bytes\": %lld}\n", (long long)(n * k * 8 + n * 4 + 2 * n * 8));
     return 0;
   }
 
