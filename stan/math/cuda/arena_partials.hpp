@@ -79,11 +79,15 @@ class arena_partials {
       operand_edge<T3>::dump(o3, varis_ + off_[2]);
       operand_edge<T4>::dump(o4, varis_ + off_[3]);
       operand_edge<T5>::dump(o5, varis_ + off_[4]);
+      for (int e = 0; e < 5; ++e) {  // small edges start from zero like operands_and_partials' (cheap insurance);
+        if (n_[e] <= 4096) {         // an N-element edge is written entirely by the device
+          zero(e);
+        }
+      }
     }
   }
   /** where the device writes the partials of edge e (0-based, in argument order); nullptr for an arithmetic
-   * operand.  Every slot the caller asks the device for is written by it; slots of edges it does not ask for must
-   * be set by the caller (zero()). */
+   * operand.  Every slot the caller asks the device for is written by it. */
   double* partials(int e) const { return n_[e] == 0 ? nullptr : partials_ + off_[e]; }
   size_t size(int e) const { return n_[e]; }
   /** sets the partials of edge e to zero (operands_and_partials starts from zeroed partials) */
