@@ -27,8 +27,10 @@ def test_cxx_binary(name):
     if not os.path.exists(exe):
         pytest.skip("%s not built (test/Makefile needs /root/reference)" % name)
     env = dict(os.environ)    # the real library, through RUNPATH: never the CPU suite's test double (build/mock)
-    env["LD_LIBRARY_PATH"] = os.pathsep.join(p for p in env.get("LD_LIBRARY_PATH", "").split(os.pathsep)
-                                             if p and os.path.join("build", "mock") not in p)
+    kept = [p for p in env.get("LD_LIBRARY_PATH", "").split(os.pathsep) if p and os.path.join("build", "mock") not in p]
+    env.pop("LD_LIBRARY_PATH", None)
+    if kept:
+        env["LD_LIBRARY_PATH"] = os.pathsep.join(kept)
     ldd = subprocess.run(["ldd", exe], stdout=subprocess.PIPE, text=True, env=env).stdout
     if "libstanmath_cuda.so" in ldd:   # (tests whose argument kinds never route to the device do not link it)
         assert os.path.join("math_b200", "lib", "libstanmath_cuda.so") in ldd, ldd
