@@ -87,3 +87,21 @@ def test_map_rect_dispatch_against_mock_device(mock_env):
     env = dict(mock_env, STAN_CUDA_MOCK_DEVICES="3", STAN_NUM_THREADS="4")
     r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300, env=env)
     assert r.returncode == 0 and "PASSED  ] 4 tests" in r.stdout, r.stdout[-3000:]
+
+
+@pytest.mark.parametrize("config", ["c1", "c2", "c3", "c4", "c5", "d1", "d2", "v2"])
+def test_stan_bench_harness_against_mock_device(mock_env, config):
+    """bench/stan_bench.cpp, every config at a small size: the harness itself (problem generation, the map_rect
+    functors, the reading of adjoints) agrees with the reference bodies it times beside the device path."""
+    import json
+    exe = os.path.join(CXX_DIR, "stan_bench")
+    if not os.path.exists(exe):
+        pytest.skip("stan_bench not built (test/Makefile needs /root/reference)")
+    env = dict(mock_env, STAN_NUM_THREADS="4")
+    n = "2000" if config == "c5" else "20000"
+    r = subprocess.run([exe, "--config", config, "--n", n, "--reps", "2", "--cpu-reps", "1"], stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    errs = [v for k, v in out.items() if k.startswith("parity_rel_err")]
+    assert errs and max(errs) <= 1e-10, out
