@@ -4,24 +4,35 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (host cores)
 
-Workload (default): BASELINE configs[2] -- poisson_log_glm_lpmf, N = 1e7 rows, K = 128 columns,
+Workload (default c3): BASELINE configs[2] -- poisson_log_glm_lpmf, N = 1e7 rows, K = 128 columns,
 synthetic X ~ N(0,1), y ~ Poisson(exp(alpha_true + X beta_true)), evaluated at a perturbed
 (alpha, beta).  One step = one evaluation = log-density + d/dalpha + d/dbeta.
 For N > 1 the rows are split evenly over the ranks (total work fixed: strong scaling) and each
-evaluation ends with an NCCL all-reduce of the K+4 result doubles.
+evaluation ends with an all-reduce of the K+4 result doubles (fused into the kernel over NVLink
+peer memory, or ncclAllReduce behind it: --collective).
 
 Numbers on the JSON line:
-  value     evaluations/s with X, y AND the parameter block resident in HBM; timed with CUDA events
-            on the launch stream, max over ranks.
+  value     evaluations/s with X, y AND the parameter block resident in HBM.  Every step is timed with
+            CUDA events on the launch stream; a step's time is the MAX over ranks; `value` = 1 / MEDIAN
+            step ("median and p10/p90").  `value_mean` / `ms_per_step_mean` come from the one
+            event pair around all K steps (max over ranks); `steps_ms` lists every step.
   e2e       the same metric through the host-level C-ABI call stan_cuda_glm_eval with HOST buffers
             for alpha/beta and the outputs: per step H2D of the parameters, kernel (+ all-reduce),
-            D2H of [lp, gradient], stream sync.  X and y are device-cached by design (the north
-            star's "caches X and y on the device the first time it sees them"); the one-time cache
-            fill is reported separately as cache_fill_ms.
-  roofline  algorithmic bytes (N*K*8 + N*4, one read of X and y) / mean kernel duration vs the
-            measured HBM copy bandwidth in MEASURED_PEAKS.json.
+            D2H of [lp, gradient].  X and y are device-cached by design (the north star's "caches X
+            and y on the device the first time it sees them"); the one-time cache fill is reported
+            separately as cache_fill_ms.
+  roofline  algorithmic bytes (N*K*8 + N*4, one read of X and y) / median kernel duration vs the
+            measured HBM copy bandwidth in MEASURED_PEAKS.json.  `traffic` is NOT a live counter: it is
+            the ncu dram bytes of the same launch from profiles/traffic.json (traffic_source says so).
   cpu_baseline  the compiled reference (oracle/_ref/libstanref.so: Stan Math + TBB map_rect on all
-            host cores) on a bounded row sample, scaled to the full N.
+            host cores) on ALL rows of the workload, a few evaluations; its result is also the parity check
+            of the full-size CUDA result (parity_rel_err_full_n).
+  parity    N > 1: every rank evaluates the CPU checker on the first rows of ITS shard, the sums over ranks
+            are compared with a sharded CUDA evaluation of exactly those rows (same collective as the
+            timed loop): multi_gpu_parity_rel_err; the run fails (rc 3) above 1e-10.
+
+Workloads c1 (vectorised normal_lpdf) and c5 (map_rect, 64 shards) run through the reference's C++
+signatures: bench.py drives build/cxx/stan_bench (bench/stan_bench.cpp) and reformats its line.
 """
 import argparse
 import json
@@ -41,8 +52,47 @@ WORKLOADS = {
     "c3": ("poisson_log", 10_000_000, 128, "poisson_log_glm_lpmf N=1e7 K=128 value+gradient (BASELINE configs[2], the metric's config)"),
     "c2": ("bernoulli_logit", 1_000_000, 32, "bernoulli_logit_glm_lpmf N=1e6 K=32 value+gradient (BASELINE configs[1])"),
     "c4": ("normal_id", 20_000_000, 256, "normal_id_glm_lpdf N=2e7 K=256 value+gradient (BASELINE configs[3])"),
+    # through the C++ signatures (build/cxx/stan_bench)
+    "c1": ("normal_lpdf", 1_000_000, 0, "normal_lpdf(y | mu, sigma) N=1e6, var vector mu, var sigma: value + reverse-mode gradient (BASELINE configs[0])"),
+    "c5": ("map_rect", 6_400_000, 32, "map_rect J=64 shards x 1e5 rows x K=32 bernoulli_logit_glm value+gradient (BASELINE configs[4])"),
 }
 FAM_ID = {"bernoulli_logit": 0, "poisson_log": 1, "normal_id": 2}
+PARITY_TOL = 1e-10
+
+
+def workload_config(desc, family, n, k, world):
+    """`config` of the JSON line.  A function of the command line only, so that both arms (--impl b200 and
+    --impl reference) print the same object for the same --gpus / --workload."""
+    rows = (n + world - 1) // world
+    return {"workload": desc, "family": family, "n": n, "k": k, "rows_per_gpu": rows,
+            "parallelism": ("rows/%d + all-reduce(sum) of the %d-double result block" % (world, k + 4)) if world > 1 else "1 GPU",
+            "l2": "no flush: per-GPU input %.2f GB is larger than the 126 MB L2" % (rows * (k * 8 + 4) / 1e9)}
+
+
+def summarize(ms):
+    """min / p10 / median / p90 / max / mean of a list of per-step times."""
+    a = np.sort(np.asarray(ms, dtype=np.float64))
+    q = lambda f: float(a[int(round(f * (len(a) - 1)))])  # noqa: E731
+    return {"min": float(a[0]), "p10": q(0.1), "median": float(np.median(a)), "p90": q(0.9), "max": float(a[-1]),
+            "mean": float(a.mean())}
+
+
+def shard_count(n, cores):
+    """Number of equal map_rect jobs for n rows (map_rect needs equal-sized jobs, map_rect.hpp:139-163): the
+    largest divisor of n in [cores, 4 * cores] so that ALL rows are evaluated; 4 * cores (a few rows dropped)
+    if n has no such divisor."""
+    for d in range(4 * cores, cores - 1, -1):
+        if n % d == 0:
+            return d
+    return 4 * cores
+
+
+def rel_err(a, b):
+    a, b = np.atleast_1d(np.asarray(a, float)), np.atleast_1d(np.asarray(b, float))
+    scale = float(np.max(np.abs(b))) if b.size else 0.0
+    den = np.maximum(np.abs(b), 1e-6 * scale)
+    den[den == 0] = 1.0
+    return float(np.max(np.abs(a - b) / den))
 
 
 def synth_shard(family, n_rows, k, seed):
@@ -75,13 +125,18 @@ class ClockSampler:
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
 
-    def start(self):
+    def start(self, wait_first_s=3.0):
+        """Starts nvidia-smi and returns once its first sample has arrived: its start-up (NVML init, a
+        fork of this process) must not fall into anybody's timed region."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            t0 = time.perf_counter()
+            while not self.lines and time.perf_counter() - t0 < wait_first_s and self.proc.poll() is None:
+                time.sleep(0.01)
         except OSError:
             self.proc = None
 
@@ -134,78 +189,158 @@ def ncu_traffic(workload):
     return None
 
 
-def cpu_reference_eval_rate(family, x, y, alpha, beta, sigma, n_full, budget_s=20.0, sample_rows=1_000_000):
-    """Times the compiled reference (Stan Math + TBB map_rect over all host cores) on the first
-    `sample_rows` rows and scales to n_full rows (the path is linear in N)."""
-    from oracle import loader as L
-    cores = os.cpu_count() or 1
-    m = min(sample_rows, x.shape[0])
-    shards = cores * 4
-    m -= m % shards
-    xs = np.asfortranarray(x[:m])
-    ys = np.ascontiguousarray(y[:m])
-    if L.have_ref():
-        sh = L.RefShards(family, xs, ys, n_shards=shards, n_threads=-1)
-        times = []
-        t_start = time.perf_counter()
-        while len(times) < 5 and (time.perf_counter() - t_start < budget_s or len(times) < 2):
-            t0 = time.perf_counter()
-            sh.eval(beta, alpha=alpha, sigma=sigma)
-            times.append(time.perf_counter() - t0)
-        threads = sh.threads
-        sh.close()
-        t0 = time.perf_counter()
-        single = L.ref_glm(family, xs, ys, alpha, beta, sigma)
-        t_single = time.perf_counter() - t0
-        t = min(times)
-        return {"value": 1.0 / (t * n_full / m), "unit": "evals/s", "cores": threads, "kind": "reference",
-                "sample": "first %d of %d rows, %d map_rect shards on %d TBB threads, best of %d; time scaled by N/sample"
-                          % (m, n_full, shards, threads, len(times)),
-                "single_thread_value": 1.0 / (t_single * n_full / m), "seconds_per_sample_eval": t,
-                "sample_lp": single["lp"]}
-    t0 = time.perf_counter()
-    L.oracle_glm(family, xs, ys, alpha, beta, sigma)
-    t = time.perf_counter() - t0
-    return {"value": 1.0 / (t * n_full / m), "unit": "evals/s", "cores": 1, "kind": "port",
-            "sample": "first %d of %d rows, plain-C oracle, 1 thread; time scaled by N/sample" % (m, n_full)}
+class CpuReference:
+    """The reference's CPU path for one GLM workload on this box's host cores: Stan Math's map_rect over
+    equal row shards on TBB threads (STAN_NUM_THREADS = all cores; oracle/ref_shim.cpp drives
+    stan/math/rev/mat/functor/map_rect_concurrent.hpp:39-54 after init_threadpool_tbb()), or -- where the
+    reference was not compiled -- the single-threaded plain-C port."""
+
+    def __init__(self, family, x, y):
+        from oracle import loader as L
+        self.L, self.family, self.x, self.y = L, family, x, y
+        n = x.shape[0]
+        self.cores = os.cpu_count() or 1
+        self.sh = None
+        if L.have_ref():
+            self.shards = shard_count(n, self.cores)
+            self.rows = n - n % self.shards
+            xs = x if self.rows == n else np.asfortranarray(x[:self.rows])
+            ys = y if self.rows == n else np.ascontiguousarray(y[:self.rows])
+            self.sh = L.RefShards(family, xs, ys, n_shards=self.shards, n_threads=-1)
+            self.kind, self.threads = "reference", self.sh.threads
+        else:
+            self.kind, self.threads, self.shards, self.rows = "port", 1, 1, n
+
+    def eval(self, alpha, beta, sigma):
+        if self.sh is not None:
+            return self.sh.eval(beta, alpha=alpha, sigma=sigma)
+        return self.L.oracle_glm(self.family, self.x, self.y, alpha, beta, sigma)
+
+    def sample(self, n):
+        if self.rows == n:
+            what = "all %d rows" % n
+        else:
+            what = "first %d of %d rows (equal-sized map_rect jobs), time scaled by N/sample" % (self.rows, n)
+        if self.kind == "reference":
+            return "%s through map_rect: %d shards on %d TBB threads" % (what, self.shards, self.threads)
+        return "%s, plain-C oracle, 1 thread" % what
+
+    def close(self):
+        if self.sh is not None:
+            self.sh.close()
+            self.sh = None
 
 
 def run_reference(args, family, n, k, desc):
+    """--impl reference: the reference's own CPU implementation of the path on ALL rows of the workload.
+    Rank 0 alone works; every evaluation is one timed step.  --steps is honoured up to a time budget
+    (steps_run says how many were timed).  Leaves through os._exit: TBB's scheduler, the reference's static
+    tape observer and ctypes are otherwise torn down in arbitrary order at interpreter exit (the SIGSEGV of
+    round 1's reference arm)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
-        return
-    sample_rows = min(n, 1_000_000)
-    x, y, alpha, beta, sigma = synth_shard(family, sample_rows, k, seed=1000)
-    from oracle import loader as L
-    cores = os.cpu_count() or 1
-    shards = cores * 4
-    m = sample_rows - sample_rows % shards
-    xs, ys = np.asfortranarray(x[:m]), np.ascontiguousarray(y[:m])
-    if L.have_ref():
-        sh = L.RefShards(family, xs, ys, n_shards=shards, n_threads=-1)
-        step = lambda b: sh.eval(b, alpha=alpha, sigma=sigma)  # noqa: E731
-        kind, threads = "reference", sh.threads
-    else:
-        step = lambda b: L.oracle_glm(family, xs, ys, alpha, b, sigma)  # noqa: E731
-        kind, threads = "port", 1
+        sys.stdout.flush()
+        os._exit(0)
+    t_gen = time.perf_counter()
+    x, y, alpha, beta, sigma = synth_shard(family, n, k, seed=1000)
+    gen_s = time.perf_counter() - t_gen
+    ref = CpuReference(family, x, y)
+    budget_s = float(os.environ.get("STAN_BENCH_REF_BUDGET_S", "120"))
     for i in range(args.warmup):
-        step(beta * (1 + 1e-3 * i))
-    t0 = time.perf_counter()
+        ref.eval(alpha, beta * (1 + 1e-3 * i), sigma)
+    times = []
+    t_start = time.perf_counter()
     for i in range(args.steps):
-        step(beta * (1 + 1e-3 * i))
-    dt = time.perf_counter() - t0
-    per_full = dt / args.steps * (n / m)
-    value = 1.0 / per_full
+        t0 = time.perf_counter()
+        ref.eval(alpha, beta * (1 + 1e-3 * i), sigma)
+        times.append(time.perf_counter() - t0)
+        if time.perf_counter() - t_start > budget_s and len(times) >= 3:
+            break
+    scale = n / ref.rows
+    st = summarize([t * 1e3 * scale for t in times])
+    value = 1e3 / st["median"]
     line = {"impl": "reference", "metric": "glm_lp_grad_evals_per_sec", "value": value, "unit": "evals/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_full * 1e3,
+            "n_gpus": args.gpus, "steps": args.steps, "steps_run": len(times), "warmup": args.warmup,
+            "ms_per_step": st["median"], "ms_per_step_stats": st, "value_mean": 1e3 / st["mean"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": desc, "n": n, "k": k, "family": family},
-            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": threads, "kind": kind,
-                             "sample": "each step = first %d of %d rows through map_rect (%d shards, %d TBB threads); "
-                                       "step time scaled by N/sample" % (m, n, shards, threads)},
+            "config": workload_config(desc, family, n, k, max(args.gpus, 1)),
+            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": ref.threads, "kind": ref.kind,
+                             "sample": "each step = " + ref.sample(n), "host_cores": os.cpu_count()},
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "data_gen_s": gen_s}
+    ref.close()
     print(json.dumps(line))
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
+
+
+# ------------------------------------------------------------------------------------------------------
+# C1 / C5 through the reference's C++ signatures (bench/stan_bench.cpp)
+# ------------------------------------------------------------------------------------------------------
+def stan_bench_exe():
+    return os.path.join(ROOT, "build", "cxx", "stan_bench")
+
+
+def run_stan_bench(config, extra=(), env=None, timeout=900):
+    exe = stan_bench_exe()
+    if not os.path.exists(exe):
+        raise SystemExit("bench.py: %s is missing (built by __graft_entry__.build() where /root/reference exists)" % exe)
+    e = dict(os.environ)
+    ld = [os.path.join(ROOT, "math_b200", "lib"), os.path.join(ROOT, "oracle", "_ref", "tbb")]
+    e["LD_LIBRARY_PATH"] = ":".join(ld + ([e["LD_LIBRARY_PATH"]] if e.get("LD_LIBRARY_PATH") else []))
+    if env:
+        e.update(env)
+    r = subprocess.run([exe, "--config", config] + list(extra), stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                       env=e, timeout=timeout)
+    if r.returncode != 0:
+        raise SystemExit("bench.py: stan_bench --config %s failed (rc %d): %s" % (config, r.returncode, r.stderr[-800:]))
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def run_cxx_workload(args, name, desc):
+    """c1 / c5: one evaluation = forward call through the unchanged C++ signature + grad() + reading every adjoint."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:   # one process drives all devices of the box (map_rect dispatches shards to devices)
+        return
+    if args.impl == "reference":
+        j = run_stan_bench(name, ["--cpu-only", "--cpu-reps", str(max(args.steps, 3))])
+        key = "cpu_reference_tbb_map_rect" if name == "c5" else "cpu_reference_1_thread"
+        t = j[key]
+        line = {"impl": "reference", "metric": "lp_grad_evals_per_sec", "value": t["evals_per_s"], "unit": "evals/s",
+                "n_gpus": args.gpus, "steps": t["reps"], "warmup": 1, "ms_per_step": t["median_ms"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": desc},
+                "cpu_baseline": {"value": t["evals_per_s"], "unit": "evals/s", "kind": "reference",
+                                 "cores": j["host_threads"] if name == "c5" else 1,
+                                 "sample": "whole workload, " + ("TBB map_rect_concurrent" if name == "c5" else "reference loop on one thread")},
+                "e2e": {"value": t["evals_per_s"], "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+    env = {"STAN_CUDA_DEVICES": str(max(args.gpus, 1))}
+    j = run_stan_bench(name, ["--reps", str(max(args.steps, 5)), "--cpu-reps", "3"], env=env)
+    if name == "c5":
+        t, tv, cpu = j["gpu_map_rect"], j["gpu_map_rect_zero_copy_view"], j["cpu_reference_tbb_map_rect"]
+        note = ("e2e = the UNMODIFIED functor (copies x_r into a MatrixXd on every call, as a Stan program does); "
+                "e2e_view = the same functor with x as cuda::data_matrix_view (= Eigen::Map<const MatrixXd>): a "
+                "one-line change of the user's functor, reported as an opt-in only")
+    else:
+        t, tv, cpu = j["gpu"], None, j["cpu_reference_1_thread"]
+        note = "forward + grad() + reading the N adjoints through stan::math::normal_lpdf"
+    line = {"metric": "lp_grad_evals_per_sec", "value": t["evals_per_s"], "unit": "evals/s", "n_gpus": max(args.gpus, 1),
+            "steps": t["reps"], "warmup": 3, "ms_per_step": t["median_ms"], "ms_per_step_stats": t,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "through": "build/cxx/stan_bench (reference C++ signatures, overlay, -DSTAN_CUDA)"},
+            "e2e": {"value": t["evals_per_s"], "unit": "evals/s", "ms_per_step": t["median_ms"], "note": note},
+            "cpu_baseline": {"value": cpu["evals_per_s"], "unit": "evals/s", "kind": "reference", "ms": cpu["median_ms"],
+                             "cores": j["host_threads"] if name == "c5" else 1, "sample": "whole workload"},
+            "parity_rel_err": j.get("parity_rel_err"), "stan_bench": j}
+    if tv:
+        line["e2e_view"] = {"value": tv["evals_per_s"], "unit": "evals/s", "ms_per_step": tv["median_ms"]}
+    print(json.dumps(line))
+    if j.get("parity_rel_err") is not None and j["parity_rel_err"] > PARITY_TOL:
+        raise SystemExit(3)
 
 
 def main():
@@ -225,6 +360,9 @@ def main():
     if args.warmup < 3:
         args.warmup = 3
     family, n, k, desc = WORKLOADS[args.workload]
+    if args.workload in ("c1", "c5"):
+        run_cxx_workload(args, args.workload, desc)
+        return
     if args.n:
         n = args.n
     if args.k:
@@ -275,6 +413,12 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(values):
+        t = torch.tensor(values, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t.cpu()]
+
     # ---- device-resident path: explicit data handle, torch-owned stream/buffers ----------------
     t0 = time.perf_counter()
     data = glm.GlmData(fam, x, y)
@@ -287,23 +431,27 @@ def main():
     stream = torch.cuda.Stream()
     sptr = stream.cuda_stream
 
-    def device_step():
-        data.launch(launch_flags, d_params.data_ptr(), d_result.data_ptr(), sptr)
+    def device_step(dh=data, res=d_result):
+        dh.launch(launch_flags, d_params.data_ptr(), res.data_ptr(), sptr)
         if world > 1 and not fused:
-            check(lib().stan_cuda_allreduce(d_result.data_ptr(), data.result_len, sptr))
+            check(lib().stan_cuda_allreduce(res.data_ptr(), dh.result_len, sptr))
 
     with torch.cuda.stream(stream):
         for _ in range(args.warmup):
             device_step()
-    barrier()
+    # every piece of rank-0-only host work (the clock sampler's start-up) happens BEFORE the barrier: with the
+    # all-reduce inside the kernel a rank that starts late is waited for INSIDE its peers' timed kernels
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    barrier()
     st0 = glm.stats()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # kernel-only events (no all-reduce) for the roofline: same loop, events around each launch
+    # one event pair per step: kev[i] brackets the kernel alone (roofline), sev[i] the whole step
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    sev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     with torch.cuda.stream(stream):
+        device_step()                 # untimed, directly in front of the timed region: lines the ranks up on the device
         ev0.record(stream)
         for i in range(args.steps):
             kev[i][0].record(stream)
@@ -311,12 +459,15 @@ def main():
             kev[i][1].record(stream)
             if world > 1 and not fused:
                 check(lib().stan_cuda_allreduce(d_result.data_ptr(), data.result_len, sptr))
+            sev[i].record(stream)
         ev1.record(stream)
     barrier()
     st1 = glm.stats()
     dev_ms = ev0.elapsed_time(ev1)
-    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
+    kernel_steps = [a.elapsed_time(b) for a, b in kev]
+    step_ms = [(ev0 if i == 0 else sev[i - 1]).elapsed_time(sev[i]) for i in range(args.steps)]
     res_dev = d_result.cpu().numpy().copy()
+    timed_launches = int(st1["kernel_launches"] - st0["kernel_launches"]) - 1   # minus the untimed line-up launch
 
     # ---- end-to-end path: host-level C-ABI call, host buffers -----------------------------------
     t0 = time.perf_counter()
@@ -326,72 +477,131 @@ def main():
     for i in range(args.warmup):
         glm.glm_eval(fam, yk, xk, alpha, beta * (1 + 1e-4 * (i + 1)), sigma, flags=flags)
     barrier()
+    e2e_steps = []
     t0 = time.perf_counter()
     for i in range(args.steps):
-        last = glm.glm_eval(fam, yk, xk, alpha, beta * (1 + 1e-4 * (i + 1)), sigma, flags=flags)
+        ts = time.perf_counter()
+        glm.glm_eval(fam, yk, xk, alpha, beta * (1 + 1e-4 * (i + 1)), sigma, flags=flags)
+        e2e_steps.append((time.perf_counter() - ts) * 1e3)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
     clocks = sampler.stop() if rank == 0 else None
 
-    # max over ranks
-    t = torch.tensor([dev_ms, e2e_s * 1e3, kernel_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms, kernel_ms = (float(v) for v in t.cpu())
+    # max over ranks, step by step
+    dev_ms, e2e_ms = max_over_ranks([dev_ms, e2e_s * 1e3])
+    step_ms = max_over_ranks(step_ms)
+    kernel_steps = max_over_ranks(kernel_steps)
+    e2e_steps = max_over_ranks(e2e_steps)
+    sst, kst, est = summarize(step_ms), summarize(kernel_steps), summarize(e2e_steps)
 
     # sanity: device-level and host-level paths agree bit for bit at the same parameters
     same = glm.glm_eval(fam, yk, xk, alpha, beta, sigma, flags=flags)
     consistent = bool(same["lp"] == res_dev[0] and np.array_equal(same["dbeta"], res_dev[4:4 + k]))
 
+    # ---- N > 1: oracle parity of the sharded evaluation (same collective as the timed loop) ------
+    parity = None
+    if world > 1:
+        from oracle import loader as L
+        m = min(rows, 100_000)
+        xs, ys = np.asfortranarray(x[:m]), np.ascontiguousarray(y[:m])
+        cpu = (L.ref_glm if L.have_ref() else L.oracle_glm)(family, xs, ys, alpha, beta, sigma)
+        mine = np.concatenate([[cpu["lp"]], np.atleast_1d(cpu["dalpha"])[:1], cpu["dbeta"][:k]])
+        tot = torch.from_numpy(mine).cuda()
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)      # plumbing: sums the CHECKER's per-rank results
+        want = tot.cpu().numpy()
+        sub = glm.GlmData(fam, xs, ys)
+        d_sub = torch.zeros(sub.result_len, dtype=torch.float64, device="cuda")
+        with torch.cuda.stream(stream):
+            device_step(sub, d_sub)
+        barrier()
+        got = d_sub.cpu().numpy()
+        parity = {"rows_per_rank": m, "checker": "compiled reference" if L.have_ref() else "plain-C oracle",
+                  "lp": rel_err(got[0], want[0]), "dalpha": rel_err(got[1], want[1]),
+                  "dbeta": rel_err(got[4:4 + k], want[2:2 + k])}
+        parity["max"] = max(parity["lp"], parity["dalpha"], parity["dbeta"])
+        parity["max"] = max_over_ranks([parity["max"]])[0]   # every rank read the same all-reduced block: must agree
+        sub.close()
+
+    rc = 0
     if rank == 0:
         peak, peak_src = measured_peak()
         alg_bytes = data.algorithmic_bytes            # this rank's shard: rows*k*8 + rows*sizeof(y)
-        achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+        achieved = alg_bytes / (kst["median"] * 1e-3) / 1e9
         line = {
-            "metric": "glm_lp_grad_evals_per_sec", "value": args.steps / (dev_ms * 1e-3), "unit": "evals/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
+            "metric": "glm_lp_grad_evals_per_sec", "value": 1e3 / sst["median"], "unit": "evals/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sst["median"],
+            "value_mean": args.steps / (dev_ms * 1e-3), "ms_per_step_mean": dev_ms / args.steps,
+            "ms_per_step_stats": sst, "steps_ms": [round(v, 5) for v in step_ms],
+            "timing": "CUDA events per step on the launch stream, max over ranks per step; value = 1 / median step; "
+                      "value_mean = K / (one event pair around all K steps, max over ranks)",
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": desc, "family": family, "n": n, "k": k, "rows_per_gpu": rows,
-                       "parallelism": ("rows/%d + %s(%d f64)" % (world, "all-reduce fused into the GLM kernel over NVLink peer memory"
-                                                                 if fused else "ncclAllReduce", data.result_len)) if world > 1 else "1 GPU",
-                       "l2": "no flush: per-GPU input %.2f GB is larger than the 126 MB L2" % (alg_bytes / 1e9)},
+            "config": workload_config(desc, family, n, k, world),
+            "collective": ("all-reduce fused into the GLM kernel over NVLink peer memory" if fused
+                           else "ncclAllReduce behind the kernel") if world > 1 else None,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(args.workload) if world == 1 and not args.n else None,
+                         "traffic": ncu_traffic(args.workload) if world == 1 and not (args.n or args.k) else None,
+                         "traffic_source": "static: ncu --set full capture of this launch (profiles/traffic.json), "
+                                           "not measured in this run",
                          "peak_source": peak_src,
                          "frac_of_nominal_8000": achieved / 8000.0,
                          "note": "peak is the pool's COPY-measured bandwidth (read + write); this kernel only reads, "
                                  "and a read-only stream can exceed it",
-                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kernel_ms,
+                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kst["median"], "kernel_ms_stats": kst,
                          "kernel": "glm_warp_kernel" if args.kernel == "warp" else "glm_fused_kernel"},
-            "e2e": {"value": args.steps / (e2e_ms * 1e-3), "unit": "evals/s",
+            "e2e": {"value": 1e3 / est["median"], "unit": "evals/s",
                     "h2d_bytes_per_step": int(data.params_len * 8), "d2h_bytes_per_step": int(data.result_len * 8),
-                    "ms_per_step": e2e_ms / args.steps,
-                    "note": "stan_cuda_glm_eval with host alpha/beta/outputs; X,y device-cached (fill timed separately)"},
-            "gpu_launches": int(st1["kernel_launches"] - st0["kernel_launches"]),
+                    "ms_per_step": est["median"], "ms_per_step_stats": est, "value_mean": args.steps / (e2e_ms * 1e-3),
+                    "note": "stan_cuda_glm_eval with host alpha/beta/outputs; X,y device-cached (fill timed separately); "
+                            "host clock per call, max over ranks, median"},
+            "gpu_launches": timed_launches,
             "clocks": clocks,
             "cache_fill_ms": cache_fill_ms, "data_create_ms": fill_ms,
             "consistent_device_vs_host_api": consistent,
             "lp": float(same["lp"]),
         }
+        if parity is not None:
+            line["multi_gpu_parity"] = parity
+            line["multi_gpu_parity_rel_err"] = parity["max"]
+            if not (parity["max"] <= PARITY_TOL):
+                rc = 3
         if world == 1 and not args.no_cpu_baseline:
             try:
-                cb = cpu_reference_eval_rate(family, x, y, alpha, beta, sigma, n)
-                # parity at the sample the CPU leg just evaluated (same rows through the CUDA path)
-                m = int(cb["sample"].split()[1])
-                if "sample_lp" in cb:
-                    xs = np.asfortranarray(x[:m])
-                    got = glm.glm_eval(fam, np.ascontiguousarray(y[:m]), xs, alpha, beta, sigma, flags=flags)
-                    cb["sample_parity_rel_err_lp"] = abs(got["lp"] - cb["sample_lp"]) / abs(cb["sample_lp"])
+                ref = CpuReference(family, x, y)
+                budget_s = float(os.environ.get("STAN_BENCH_CPU_BUDGET_S", "25"))
+                times, t_start = [], time.perf_counter()
+                while len(times) < 5 and (time.perf_counter() - t_start < budget_s or len(times) < 2):
+                    t0 = time.perf_counter()
+                    out = ref.eval(alpha, beta, sigma)
+                    times.append(time.perf_counter() - t0)
+                cst = summarize([t * 1e3 * n / ref.rows for t in times])
+                cb = {"value": 1e3 / cst["median"], "unit": "evals/s", "cores": ref.threads, "kind": ref.kind,
+                      "sample": ref.sample(n) + "; %d evaluations, median" % len(times), "ms_stats": cst,
+                      "host_cores": os.cpu_count()}
+                if ref.rows == n:   # the checker saw every row: full-size parity of the CUDA result
+                    e = {"lp": rel_err(res_dev[0], out["lp"]), "dbeta": rel_err(res_dev[4:4 + k], out["dbeta"][:k]),
+                         "dalpha": rel_err(res_dev[1], np.atleast_1d(out["dalpha"])[0])}
+                    line["parity_rel_err_full_n"] = e
+                    if not (max(e.values()) <= PARITY_TOL):
+                        rc = 3
+                ref.close()
                 line["cpu_baseline"] = cb
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"error": repr(e)}
         print(json.dumps(line))
+        sys.stdout.flush()
     data.close()
     glm.cache_clear()
     if world > 1:
         lib().stan_cuda_comm_destroy()
         dist.destroy_process_group()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # the CPU leg started TBB and the reference's static tape observer: same teardown hazard as the reference arm
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(rc)
+    if rc:
+        raise SystemExit(rc)
 
 
 if __name__ == "__main__":

@@ -419,7 +419,8 @@ def test_full_size_c3_row_additivity_and_sample_parity(glm, L, request):
     full = _raw_eval(glm, _abi.POISSON_LOG, x.ctypes.data, n, n, k, y.ctypes.data, alpha[0], beta)
     from tests import config_cases as cc
     golden, man = cc.load()                      # outputs of the compiled reference on these same inputs
-    if cc.inputs_reproduce(man, "c3", x, y):
+    reproduced = cc.inputs_reproduce(man, "c3", x, y)
+    if reproduced:
         assert_close(full[0], golden["c3/lp"][0], "C3 lp vs compiled reference")
         assert_close(full[1], golden["c3/dbeta"], "C3 dbeta vs compiled reference")
         assert_close(full[2], golden["c3/dalpha"][0], "C3 dalpha vs compiled reference")
@@ -435,6 +436,9 @@ def test_full_size_c3_row_additivity_and_sample_parity(glm, L, request):
     got = glm.glm_eval("poisson_log", ys, xs, alpha, beta)
     check_glm_result(got, ref, "rows sampled from C3")
     glm.cache_clear()
+    if not reproduced:   # the additivity and sampled-row checks above ran; say loudly that the 1e-10 check did not
+        pytest.skip("this host does not regenerate the stored C3 inputs bit for bit: comparison with the stored "
+                    "outputs of the compiled reference NOT run (additivity and sampled-row parity passed)")
 
 
 def test_device_level_launch_matches_host_level(glm):
