@@ -112,6 +112,7 @@ extern "C" {
 #define STAN_CUDA_NEED_DCUTS 0x20u  /* ordered_logistic: d/dcuts (shares the bit of NEED_DSIGMA)  */
 #define STAN_CUDA_NEED_DY 0x40u
 #define STAN_CUDA_NEED_ALL 0x78u
+#define STAN_CUDA_NEED_DX 0x400u    /* d/dx = d * beta^T (n x k), var x */
 /* stan_cuda_glm_launch only: sum the result block over the ranks of the communicator INSIDE the
  * fused kernel (peer exchange over NVLink, see stan_cuda_comm_fused_available) instead of a
  * separate stan_cuda_allreduce.  Every rank must launch with the flag, in the same order. */
@@ -147,6 +148,16 @@ typedef struct stan_cuda_glm_args {
    * n_classes entries (alpha_len = n_classes), beta is k x n_classes column-major, dalpha[n_classes],
    * dbeta[k * n_classes] */
   int64_t n_classes;
+  /* 1: y is not immutable data -- a var outcome vector (normal_id_glm_lpdf with y a parameter), or a scalar
+   * outcome the wrapper broadcasts into a temporary.  The cache is then keyed on x ALONE and y travels to the
+   * device with every call (its range and sum lgamma(y + 1) are recomputed per call), so x is never refilled. */
+  int32_t y_per_call;
+  int32_t reserved0;
+  /* var x (bernoulli_logit_glm_lpmf.hpp:125-128, poisson_log_glm_lpmf.hpp:119-122,
+   * normal_id_glm_lpdf.hpp:121-124): with STAN_CUDA_NEED_DX the kernel also streams out
+   * d/dx[i][j] = d_i * beta_j, column-major n x k with leading dimension lddx (>= n), host memory. */
+  double* dx;
+  int64_t lddx;
 } stan_cuda_glm_args;
 
 typedef struct stan_cuda_normal_args {
@@ -252,6 +263,15 @@ STAN_CUDA_API int64_t stan_cuda_cache_bytes(void);                  /* device by
  * 0 = automatic: 80 % of the smallest device's memory, or environment STAN_CUDA_CACHE_BYTES.
  * (matrix_cl has no counterpart: its buffers live as long as the C++ object, stan/math/opencl/matrix_cl.hpp:32-454.) */
 STAN_CUDA_API void stan_cuda_cache_set_limit(int64_t bytes);
+/* Cache identity.  Outside a shard scope an entry is found by (x pointer, y pointer, shape, layout) and is
+ * trusted only if a content fingerprint of 64 sampled elements of x and of y still matches; inside a scope by
+ * (call_id, job, ordinal of the GLM call inside the job, shape, family) plus a 16-sample tripwire.  A host
+ * array that is REWRITTEN IN PLACE at positions the samples miss is not noticed: data handed to these entry
+ * points is immutable by contract (a Stan program's data block; x_r / x_i of map_rect,
+ * stan/math/prim/mat/functor/map_rect.hpp:97-100) -- call stan_cuda_cache_invalidate after mutating it.
+ * verify = 1 (or environment STAN_CUDA_CACHE_VERIFY=1) replaces the samples by a hash of EVERY element of x
+ * and y on every call: O(n k) host work per evaluation, for debugging and for the test-suite. */
+STAN_CUDA_API void stan_cuda_cache_set_verify(int verify);
 
 /* ---- map_rect shard scope (thread-local) ---------------------------------------------------- */
 /* Inside a scope, evaluations of the calling thread run on `device` and their data is keyed by

@@ -20,6 +20,7 @@ LP_CONST, LP_SCALE, LP_MAIN, LP_ALL = 0x01, 0x02, 0x04, 0x07
 LP_LINEAR = 0x200
 NEED_DBETA, NEED_DALPHA, NEED_DSIGMA, NEED_DY, NEED_ALL = 0x08, 0x10, 0x20, 0x40, 0x78
 NEED_DCUTS = 0x20
+NEED_DX = 0x400
 FUSED_ALLREDUCE = 0x100
 
 c_double_p = C.POINTER(C.c_double)
@@ -51,6 +52,10 @@ class GlmArgs(C.Structure):
         ("cuts_len", C.c_int64),
         ("dcuts", C.c_void_p),
         ("n_classes", C.c_int64),
+        ("y_per_call", C.c_int32),
+        ("reserved0", C.c_int32),
+        ("dx", C.c_void_p),
+        ("lddx", C.c_int64),
     ]
 
 
@@ -126,6 +131,7 @@ PROTOTYPES = {
     "stan_cuda_cache_clear": (None, []),
     "stan_cuda_cache_set_limit": (None, [C.c_int64]),
     "stan_cuda_cache_bytes": (C.c_int64, []),
+    "stan_cuda_cache_set_verify": (None, [C.c_int]),
     "stan_cuda_shard_scope_enter": (None, [C.c_int, C.c_int, C.c_int]),
     "stan_cuda_shard_scope_exit": (None, []),
     "stan_cuda_comm_unique_id": (C.c_int, [C.c_void_p]),

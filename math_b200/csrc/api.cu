@@ -93,6 +93,7 @@ static void make_room_locked(int64_t incoming) {
 struct Scope {
   bool active = false;
   int call_id = 0, job = 0, device = 0;
+  int ordinal = 0;  // GLM calls made inside this scope so far: the n-th call of a job is a different data set than the first
 };
 static thread_local Scope tl_scope;
 
@@ -112,7 +113,53 @@ static inline uint64_t fnv(uint64_t h, uint64_t v) {
 // map_rect shard scope the identity is (call_id, job) and immutability is map_rect's own contract
 // (stan/math/prim/mat/functor/map_rect.hpp:97-100), so 4 samples per array (first, last, two in between) remain as
 // a tripwire only: the 128 scattered host reads per evaluation cost more than the launch of a 26 MB shard.
-static uint64_t fingerprint_glm(const stan_cuda_glm_args* a, int64_t samples) {
+static std::atomic<int> g_cache_verify{-1};  // -1: read STAN_CUDA_CACHE_VERIFY on first use
+static bool cache_verify() {
+  int v = g_cache_verify.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("STAN_CUDA_CACHE_VERIFY");
+    v = (e && *e && *e != '0') ? 1 : 0;
+    g_cache_verify.store(v, std::memory_order_relaxed);
+  }
+  return v != 0;
+}
+
+// Hash of EVERY element (verify mode): four independent chains so the multiplies overlap.
+static uint64_t hash_words(const void* base, int64_t words8, uint64_t h) {
+  const unsigned char* p = static_cast<const unsigned char*>(base);
+  uint64_t h0 = h, h1 = h ^ 0x1111111111111111ull, h2 = h ^ 0x2222222222222222ull, h3 = h ^ 0x3333333333333333ull;
+  int64_t i = 0;
+  for (; i + 4 <= words8; i += 4) {
+    uint64_t w[4];
+    memcpy(w, p + i * 8, 32);
+    h0 = fnv(h0, w[0]); h1 = fnv(h1, w[1]); h2 = fnv(h2, w[2]); h3 = fnv(h3, w[3]);
+  }
+  for (; i < words8; ++i) {
+    uint64_t w;
+    memcpy(&w, p + i * 8, 8);
+    h0 = fnv(h0, w);
+  }
+  return fnv(fnv(fnv(h0, h1), h2), h3);
+}
+
+static uint64_t fingerprint_glm_full(const stan_cuda_glm_args* a, bool with_y) {
+  uint64_t h = 1469598103934665603ull;
+  const int64_t outer = a->x_row_major ? a->n : a->k, inner = a->x_row_major ? a->k : a->n;
+  for (int64_t o = 0; o < outer; ++o) h = hash_words(a->x + o * a->ldx, inner, h);
+  if (with_y) {
+    if (a->y_is_double) {
+      h = hash_words(a->y, a->n, h);
+    } else {
+      const int32_t* y = static_cast<const int32_t*>(a->y);
+      h = hash_words(y, a->n / 2, h);
+      if (a->n & 1) h = fnv(h, uint64_t(uint32_t(y[a->n - 1])));
+    }
+  }
+  return h;
+}
+
+static uint64_t fingerprint_glm(const stan_cuda_glm_args* a, int64_t samples, bool with_y) {
+  if (cache_verify()) return fingerprint_glm_full(a, with_y);
   uint64_t h = 1469598103934665603ull;
   const int64_t cnt = a->n * a->k;
   const int64_t step = cnt > samples ? (cnt - 1) / (samples - 1) : 1;
@@ -125,7 +172,7 @@ static uint64_t fingerprint_glm(const stan_cuda_glm_args* a, int64_t samples) {
     h = fnv(h, bits);
   }
   const int64_t ystep = a->n > samples ? (a->n - 1) / (samples - 1) : 1;
-  for (int64_t i = 0; i < a->n; i += ystep) {
+  for (int64_t i = 0; with_y && i < a->n; i += ystep) {
     uint64_t bits = 0;
     if (a->y_is_double) memcpy(&bits, static_cast<const double*>(a->y) + i, 8);
     else bits = uint64_t(uint32_t(static_cast<const int32_t*>(a->y)[i]));
@@ -161,13 +208,20 @@ static std::vector<int> pick_devices(int64_t n, int64_t k) {
 
 static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* out) {
   Key key;
+  const bool with_y = !a->y_per_call;  // a per-call y is no part of the identity: keyed on x alone
+  const int64_t kind_bits = int64_t(a->family) * 8 + (a->y_per_call ? 4 : 0) + a->x_row_major * 2 + a->y_is_double +
+                            64 * tuning().layout + 256 * tuning().cat_mma;
   if (tl_scope.active) {
-    key = Key(1, uintptr_t(tl_scope.call_id), uintptr_t(tl_scope.job), a->n, a->k, a->family, tl_scope.device);
+    // (call_id, job) is the identity of a job's immutable data (mpi_parallel_call.hpp:40-89); a functor may make
+    // SEVERAL GLM calls per job (one design matrix, two outcome vectors ...): the ordinal of the call inside the
+    // job tells them apart (a functor runs the same sequence of calls on every evaluation of the job)
+    const int ordinal = tl_scope.ordinal++;
+    key = Key(1, uintptr_t(uint32_t(tl_scope.call_id)) | (uintptr_t(uint32_t(ordinal)) << 32), uintptr_t(tl_scope.job), a->n,
+              a->k, kind_bits, tl_scope.device);
   } else {
-    key = Key(0, uintptr_t(a->x), uintptr_t(a->y), a->n, a->k, a->ldx,
-              int64_t(a->family) * 4 + a->x_row_major * 2 + a->y_is_double + 64 * tuning().layout + 256 * tuning().cat_mma);
+    key = Key(0, uintptr_t(a->x), with_y ? uintptr_t(a->y) : uintptr_t(0), a->n, a->k, a->ldx, kind_bits);
   }
-  const uint64_t fp = fingerprint_glm(a, tl_scope.active ? 4 : 64);
+  const uint64_t fp = fingerprint_glm(a, tl_scope.active ? 16 : 64, with_y);
   std::lock_guard<std::mutex> lk(g_cache_mu);
   auto it = g_cache.find(key);
   if (it != g_cache.end() && it->second->fingerprint == fp) {
@@ -255,6 +309,8 @@ struct ShardRun {
   ThreadDev* td = nullptr;
   double *d_params = nullptr, *d_result = nullptr, *d_alpha = nullptr, *d_sigma = nullptr, *d_rowa = nullptr,
          *d_rows = nullptr;
+  void* d_y = nullptr;        // per-call outcomes (y_per_call)
+  double y_lgamma_sum = 0.0;
 };
 
 int glm_eval(const stan_cuda_glm_args* a) {
@@ -277,6 +333,33 @@ int glm_eval(const stan_cuda_glm_args* a) {
   std::shared_ptr<Entry> e;
   SC_TRY(get_glm_entry(a, &e));
   const size_t S = e->shards.size();
+  std::vector<ShardRun> runs(S);
+  // Per-call outcomes: y goes to the device now (padded to whole tiles like the cached copy) into a buffer of
+  // its own; integer outcomes also get their range and sum lgamma(y + 1) recomputed.
+  int64_t call_lo = INT64_MAX, call_hi = INT64_MIN;
+  if (a->y_per_call) {
+    const size_t ysz = a->y_is_double ? sizeof(double) : sizeof(int32_t);
+    for (size_t s = 0; s < S; ++s) {
+      stan_cuda_data* d = e->shards[s].d;
+      ShardRun& run = runs[s];
+      SC_TRY(thread_dev(d->device, &run.td));
+      SC_CUDA(cudaSetDevice(d->device));
+      const size_t padded = size_t(d->t.tiles) * d->t.R * ysz, used = size_t(d->n) * ysz;
+      SC_TRY(run.td->reserve_y((padded + 15) / 16 * 2));
+      run.d_y = run.td->d_ybuf;
+      SC_CUDA(cudaMemcpyAsync(run.d_y, static_cast<const char*>(a->y) + size_t(e->shards[s].row0) * ysz, used,
+                              cudaMemcpyHostToDevice, run.td->stream));
+      if (padded > used)
+        SC_CUDA(cudaMemsetAsync(static_cast<char*>(run.d_y) + used, 0, padded - used, run.td->stream));
+      if (!a->y_is_double) {
+        const int want_lg = a->family == STAN_CUDA_POISSON_LOG || a->family == STAN_CUDA_NEG_BINOMIAL_2_LOG;
+        int64_t lo = 0, hi = 0;
+        SC_TRY(int_vector_stats(static_cast<const int*>(run.d_y), d->n, want_lg, run.td->stream, &run.y_lgamma_sum, &lo, &hi));
+        call_lo = std::min(call_lo, lo);
+        call_hi = std::max(call_hi, hi);
+      }
+    }
+  }
   // eager domain check of the outcomes (bernoulli_logit_glm_lpmf.hpp:70, poisson_log_glm_lpmf.hpp:70)
   // from the range computed at fill: no O(N) host loop per call
   if (a->family != STAN_CUDA_NORMAL_ID) {
@@ -285,12 +368,20 @@ int glm_eval(const stan_cuda_glm_args* a) {
       lo = std::min(lo, e->shards[s].d->y_min);
       hi = std::max(hi, e->shards[s].d->y_max);
     }
-    if (ordered) {  // ordered_logistic_glm_lpmf.hpp:78 check_bounded(y, 1, N_classes)
-      if (lo < 1 || hi > int64_t(ncuts) + 1) return STAN_CUDA_BAD_OUTCOME;
-    } else if (categorical) {  // categorical_logit_glm_lpmf.hpp:63-64
-      if (lo < 1 || hi > int64_t(ncls)) return STAN_CUDA_BAD_OUTCOME;
-    } else if (lo < 0 || (a->family == STAN_CUDA_BERNOULLI_LOGIT && hi > 1)) {
+    if (a->y_per_call) {
+      lo = call_lo;
+      hi = call_hi;
+    }
+    const auto bad_outcome = [&]() {
+      if (tl_scope.active && tl_scope.ordinal > 0) --tl_scope.ordinal;  // the wrapper's retry is the same call of the job
       return STAN_CUDA_BAD_OUTCOME;
+    };
+    if (ordered) {  // ordered_logistic_glm_lpmf.hpp:78 check_bounded(y, 1, N_classes)
+      if (lo < 1 || hi > int64_t(ncuts) + 1) return bad_outcome();
+    } else if (categorical) {  // categorical_logit_glm_lpmf.hpp:63-64
+      if (lo < 1 || hi > int64_t(ncls)) return bad_outcome();
+    } else if (lo < 0 || (a->family == STAN_CUDA_BERNOULLI_LOGIT && hi > 1)) {
+      return bad_outcome();
     }
   }
   const bool alpha_vec = !ordered && !categorical && a->alpha_len != 1;
@@ -318,7 +409,6 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (xchg) xchg_seq = ++xchg->seq;
   }
 
-  std::vector<ShardRun> runs(S);
   const int kpad = e->shards[0].d->t.kpad;
   if (categorical && ncls * size_t(kpad) > size_t(kMaxClassWeights))
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit supports classes * k_pad <= 4096 on the device");
@@ -376,6 +466,8 @@ int glm_eval(const stan_cuda_glm_args* a) {
     io.ncuts = int(ncuts);
     io.ncls = int(ncls);
     io.shared_gpu = tl_scope.active;
+    io.d_y = run.d_y;
+    io.y_lgamma_sum = run.y_lgamma_sum;
     if (xchg) {
       io.xchg = S > 1 ? &xchg[s] : xchg;
       io.xchg_seq = xchg_seq;
@@ -466,7 +558,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     a->aux[0] = res[1];
     a->aux[1] = res[3];
     a->aux[2] = 0.0;
-    a->aux[3] = e->shards[0].d->lgamma_sum;
+    a->aux[3] = a->y_per_call ? runs[0].y_lgamma_sum : e->shards[0].d->lgamma_sum;
   }
   counters().evals.fetch_add(1, std::memory_order_relaxed);
   return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
@@ -511,6 +603,7 @@ int glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int*
       tl_scope.call_id = call_id;
       tl_scope.job = i;
       tl_scope.device = i % G;
+      tl_scope.ordinal = 0;
       rc = get_glm_entry(&items[i], &ents[size_t(i)]);
     }
     tl_scope = saved;
@@ -895,7 +988,11 @@ int stan_cuda_cache_invalidate(const void* host_ptr) {
   for (auto it = g_cache.begin(); it != g_cache.end();) {
     const Key& k = it->first;
     const bool by_ptr = std::get<0>(k) != 1;
-    if (by_ptr && (std::get<1>(k) == uintptr_t(host_ptr) || std::get<2>(k) == uintptr_t(host_ptr))) {
+    // inside a shard scope the entries of the CURRENT job (every call ordinal) are dropped: their identity is
+    // (call_id, job), not a pointer
+    const bool scope_hit = !by_ptr && tl_scope.active && uint32_t(std::get<1>(k)) == uint32_t(tl_scope.call_id) &&
+                           std::get<2>(k) == uintptr_t(tl_scope.job);
+    if (scope_hit || (by_ptr && (std::get<1>(k) == uintptr_t(host_ptr) || std::get<2>(k) == uintptr_t(host_ptr)))) {
       it = g_cache.erase(it);
       ++dropped;
     } else {
@@ -909,6 +1006,8 @@ void stan_cuda_cache_clear(void) {
   std::lock_guard<std::mutex> lk(g_cache_mu);
   g_cache.clear();
 }
+
+void stan_cuda_cache_set_verify(int verify) { g_cache_verify.store(verify ? 1 : 0, std::memory_order_relaxed); }
 
 void stan_cuda_cache_set_limit(int64_t bytes) {
   std::lock_guard<std::mutex> lk(g_cache_mu);
@@ -935,6 +1034,7 @@ void stan_cuda_shard_scope_enter(int call_id, int job, int device) {
   tl_scope.call_id = call_id;
   tl_scope.job = job;
   tl_scope.device = device < 0 ? 0 : device;
+  tl_scope.ordinal = 0;
 }
 
 void stan_cuda_shard_scope_exit(void) {

@@ -119,6 +119,13 @@ struct LaunchIO {
   // d_result = [lp, 0, 0, status, dalpha(ncls), dbeta: ncls rows of kpad]
   int ncls = 0;
   bool shared_gpu = false;  // other launches are expected to run concurrently on this device (map_rect shard scope)
+  // per-call outcomes (stan_cuda_glm_args.y_per_call): device vector padded to tiles * R elements that replaces the
+  // cached y of the data block for this launch, with its own sum lgamma(y + 1); no histogram of y is available
+  const void* d_y = nullptr;
+  double y_lgamma_sum = 0.0;
+  // var x: d/dx = d * beta^T streamed out tile by tile (device matrix, column-major rows x k, leading dimension ld_dx)
+  double* d_dx = nullptr;
+  int64_t ld_dx = 0;
 };
 constexpr int kMaxClasses = 16;              // categorical_logit: classes on the device path
 constexpr int kMaxClassWeights = 4096;       // categorical_logit: classes * k_pad (weights live in shared memory)

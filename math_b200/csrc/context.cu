@@ -152,6 +152,21 @@ int ThreadDev::reserve_dev(size_t doubles) {
   return STAN_CUDA_OK;
 }
 
+int ThreadDev::reserve_y(size_t doubles) {
+  if (doubles <= d_ycap) return STAN_CUDA_OK;
+  SC_CUDA(cudaSetDevice(device));
+  if (d_ybuf) {
+    SC_CUDA(cudaStreamSynchronize(stream));
+    SC_CUDA(cudaFree(d_ybuf));
+  }
+  d_ybuf = nullptr;
+  d_ycap = 0;
+  const size_t cap = doubles < 4096 ? 4096 : doubles + doubles / 4;
+  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_ybuf), cap * sizeof(double)));
+  d_ycap = cap;
+  return STAN_CUDA_OK;
+}
+
 int workspace_reserve(Workspace* w, int device, size_t doubles) {
   if (w->device == device && w->scratch && doubles <= w->scratch_doubles) return STAN_CUDA_OK;
   SC_CUDA(cudaSetDevice(device));

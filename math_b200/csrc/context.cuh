@@ -24,9 +24,12 @@ struct ThreadDev {
   unsigned long long host_seq = 0;  // completion-flag sequence of the low-latency path (api.cu)
   double* d_buf = nullptr;
   size_t d_cap = 0;  // doubles
+  double* d_ybuf = nullptr;  // per-call outcome vector (stan_cuda_glm_args.y_per_call), separate from d_buf
+  size_t d_ycap = 0;         // doubles
   Workspace ws;
   int reserve_host(size_t doubles);
   int reserve_dev(size_t doubles);
+  int reserve_y(size_t doubles);
 };
 int thread_dev(int device, ThreadDev** out);
 

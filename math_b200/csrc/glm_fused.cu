@@ -365,7 +365,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->cat_groups = 1;
   if (p->ncuts < 0 || p->ncuts > kMaxCuts) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
   p->x = d->x;
-  p->y = d->y;
+  p->y = io.d_y ? io.d_y : d->y;
   p->n = d->n;
   p->tiles = int(t.tiles);
   p->R = t.R; p->C = t.C; p->kc = t.kc; p->kpad = t.kpad;
@@ -382,7 +382,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->ticket = ws->ticket;
   p->result = io.d_result;
   p->flags = io.flags;
-  p->lgamma_sum = d->lgamma_sum;
+  p->lgamma_sum = io.d_y ? io.y_lgamma_sum : d->lgamma_sum;
   p->inline_n = 0;
   p->host_flag = io.host_flag;
   p->host_seq = io.host_seq;

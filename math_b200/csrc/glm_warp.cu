@@ -453,7 +453,7 @@ static int prepare_neg_binomial(const stan_cuda_data* d, const LaunchIO& io, Wor
                                 cudaStream_t stream) {
   p->nb_sums = nullptr;
   p->nb_rowfun = 1;
-  if (io.d_sigma_vec || !d->hist) return STAN_CUDA_OK;  // vector phi, or outcomes too large for a histogram
+  if (io.d_sigma_vec || !d->hist || io.d_y) return STAN_CUDA_OK;  // vector phi, outcomes too large for a histogram, or per-call outcomes
   double* out = ws->scratch + ws->scratch_doubles - 2;  // last two doubles of the workspace
   const bool inl = p->inline_n > 0;
   nb_hist_sums_kernel<<<1, 256, 0, stream>>>(d->hist, d->hist_len, io.d_params, d->t.kpad + 1,

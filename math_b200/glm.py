@@ -124,8 +124,9 @@ def glm_flags(family, propto, alpha_var=True, beta_var=True, sigma_var=True, y_v
     return f
 
 
-def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, need_dy=False):
-    """Raw C-ABI call (no argument checks beyond shapes).  Returns dict with rc, lp and partials."""
+def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, need_dy=False, y_per_call=False):
+    """Raw C-ABI call (no argument checks beyond shapes).  Returns dict with rc, lp and partials.
+    y_per_call: y is not immutable data (a parameter vector): cache keyed on x alone, y uploaded every call."""
     fam = _abi.FAMILIES[family] if isinstance(family, str) else family
     x, row_major, ldx = _prep_x(x)
     n, k = x.shape
@@ -147,6 +148,7 @@ def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, ne
     a.family, a.flags, a.n, a.k = fam, flags, n, k
     a.x, a.ldx, a.x_row_major = x.ctypes.data, ldx, row_major
     a.y, a.y_is_double = y.ctypes.data, int(fam == _abi.NORMAL_ID)
+    a.y_per_call = int(bool(y_per_call))
     a.alpha, a.alpha_len, a.beta = alpha.ctypes.data, alpha.size, beta.ctypes.data
     if sigma is not None:
         a.sigma, a.sigma_len = sigma.ctypes.data, sigma.size

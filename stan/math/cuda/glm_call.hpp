@@ -57,7 +57,24 @@ class glm_call {
    * outcome check, which throws).  Failures of the device layer throw std::system_error.
    */
   int run(const char* function) {
+    // A scalar weight broadcast to K != 1 columns has ONE partials slot (the caller pointed dbeta at it): the
+    // device's K components are received in a temporary and summed into that slot, instead of being copied
+    // over the neighbouring arena memory.
+    double* const caller_dbeta = a_.dbeta;
+    std::vector<double> dbeta_wide;
+    if (!beta_bcast_.empty() && caller_dbeta != nullptr && a_.k != 1) {
+      dbeta_wide.assign(a_.k, 0.0);
+      a_.dbeta = dbeta_wide.data();
+    }
     const int rc = stan_cuda_glm_eval(&a_);
+    if (!dbeta_wide.empty()) {
+      double sum = 0.0;
+      for (size_t j = 0; j < dbeta_wide.size(); ++j) {
+        sum += dbeta_wide[j];
+      }
+      *caller_dbeta = sum;
+      a_.dbeta = caller_dbeta;
+    }
     check_cuda_rc(function, rc);
     return rc;
   }

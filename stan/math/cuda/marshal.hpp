@@ -192,6 +192,10 @@ class real_outcome {
     }
   }
   const double* data() const { return ptr_; }
+  /** true when the doubles live in a temporary of this call (a var outcome vector, a broadcast scalar): their
+   * address is no identity and their content may change from call to call, so the device cache is keyed on x
+   * alone and y travels with every call (stan_cuda_glm_args.y_per_call) */
+  bool per_call() const { return !vals_.borrowed() || ptr_ != vals_.data(); }
 
  private:
   values<T> vals_;
@@ -208,6 +212,7 @@ class int_outcome<int> {
  public:
   int_outcome(const int& y, size_t n) : owned_(n, y) {}
   const int* data() const { return owned_.data(); }
+  bool per_call() const { return true; }  // a temporary: see real_outcome::per_call
 
  private:
   std::vector<int> owned_;
@@ -218,6 +223,7 @@ class int_outcome<std::vector<int>> {
  public:
   int_outcome(const std::vector<int>& y, size_t /*n*/) : ptr_(y.data()) {}
   const int* data() const { return ptr_; }
+  bool per_call() const { return false; }
 
  private:
   const int* ptr_;
@@ -228,6 +234,7 @@ class int_outcome<Eigen::Matrix<int, R, C, O, MR, MC>> {
  public:
   int_outcome(const Eigen::Matrix<int, R, C, O, MR, MC>& y, size_t /*n*/) : ptr_(y.data()) {}
   const int* data() const { return ptr_; }
+  bool per_call() const { return false; }
 
  private:
   const int* ptr_;

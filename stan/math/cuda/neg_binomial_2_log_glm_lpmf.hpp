@@ -61,6 +61,7 @@ return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(c
   arena_partials<double, T_alpha, T_beta, T_precision> ops_partials(x_placeholder, alpha, beta, phi);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
+  a.y_per_call = y_val.per_call() ? 1 : 0;
   a.y_is_double = 0;
   a.sigma = phi_val.data();
   a.sigma_len = phi_val.size();

@@ -52,6 +52,7 @@ return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y
   arena_partials<T_y, double, T_alpha, T_beta, T_scale> ops_partials(y, x_placeholder, alpha, beta, sigma);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
+  a.y_per_call = y_val.per_call() ? 1 : 0;
   a.y_is_double = 1;
   a.sigma = sigma_val.data();
   a.sigma_len = sigma_val.size();

@@ -50,6 +50,7 @@ return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T
   arena_partials<double, T_alpha, T_beta> ops_partials(x_placeholder, alpha, beta);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
+  a.y_per_call = y_val.per_call() ? 1 : 0;
   a.y_is_double = 0;
   a.flags = 0;
   if (include_summand<propto>::value) {

@@ -183,6 +183,7 @@ int stan_cuda_cache_invalidate(const void* host_ptr) {
 }
 void stan_cuda_cache_clear(void) {}
 int64_t stan_cuda_cache_bytes(void) { return 0; }
+void stan_cuda_cache_set_verify(int verify) { (void)verify; }
 
 /* scopes nest, as in the product (api.cu): exit restores the scope current at the matching enter */
 static __thread int tl_saved[8][4];

@@ -36,7 +36,7 @@ def test_library_exports_every_declared_symbol(cdll):
 
 def test_struct_layout_matches_header(cdll):
     # sizes implied by the header's field order on LP64
-    assert ctypes.sizeof(_abi.GlmArgs) == 4 + 4 + 8 + 8 + 8 + 8 + 4 + 4 + 8 * 16
+    assert ctypes.sizeof(_abi.GlmArgs) == 4 + 4 + 8 + 8 + 8 + 8 + 4 + 4 + 8 * 16 + 4 + 4 + 8 + 8
     assert ctypes.sizeof(_abi.NormalArgs) == 4 + 4 + 8 * 11
     assert ctypes.sizeof(_abi.Stats) == 8 * 9
 
