@@ -17,7 +17,9 @@ CXX_DIR = os.path.join(ROOT, "build", "cxx")
 BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_poisson_log_glm_lpmf_test",
             "ref_normal_id_glm_lpdf_test", "ref_neg_binomial_2_log_glm_lpmf_test", "ref_ordered_logistic_glm_lpmf_test", "ref_categorical_logit_glm_lpmf_test", "ref_operands_and_partials_test", "ref_precomputed_gradients_test",
             "ref_map_rect_concurrent_test", "cuda_int_density_distr_test", "ref_bernoulli_logit_log_test",
-            "ref_poisson_log_log_test", "ref_bernoulli_logit_test", "ref_poisson_log_test"]
+            "ref_poisson_log_log_test", "ref_bernoulli_logit_test", "ref_poisson_log_test",
+            "cuda_normal_distr_test", "ref_map_rect_concurrent_threads_test", "ref_map_rect_prim_test",
+            "ref_map_rect_concurrent_prim_test", "ref_normal_log_test", "ref_normal_test"]
 
 
 @pytest.mark.gpu
