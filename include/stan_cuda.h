@@ -327,6 +327,20 @@ STAN_CUDA_API int stan_cuda_glm_launch_ordered(stan_cuda_data_t d, uint32_t flag
  * d_result = [lp, 0, 0, status, dalpha(n_classes), dbeta as n_classes rows of k_pad]. */
 STAN_CUDA_API int stan_cuda_glm_launch_categorical(stan_cuda_data_t d, uint32_t flags, const double* d_params,
                                      int n_classes, double* d_result, void* stream);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same evaluation and
+ * the same argument meaning as stan_cuda_glm_launch for bernoulli_logit / poisson_log / normal_id data with a scalar
+ * intercept / scale (no per-row operands, no collective), but the call allocates NOTHING: the reduction scratch of
+ * the kernel (per-CTA partials, group sums, ticket words) lives in a file-scope __device__ array of the library,
+ * 320 x 520 doubles = 1.27 MiB (+ 256 B of tickets) that every GPU which loads the library holds until exit.
+ * Limit: (CTAs + reduction groups) x (k_pad + 4) + 2 <= 166400 doubles, i.e. every k <= 512 on a GPU of up to
+ * 160 SMs; beyond it the call returns STAN_CUDA_ERR_ARG with the two numbers in stan_cuda_last_error().
+ * Every call on a device shares that one array: calls that OVERLAP on a GPU (two streams, two host threads) race
+ * on it -- the caller serialises them.  The data handle, d_params and d_result are the caller's (created before
+ * the no-allocation region); the first call per device resolves the array's device address (cudaGetSymbolAddress),
+ * so make one call before starting a graph capture. */
+STAN_CUDA_API int stan_cuda_glm_launch_noalloc(stan_cuda_data_t d, uint32_t flags, const double* d_params,
+                                               double* d_result, void* stream);
 /* All-reduce (sum) `count` doubles in place across the ranks of the communicator, on `stream`. */
 STAN_CUDA_API int stan_cuda_allreduce(double* d_buf, int64_t count, void* stream);
 /* Number of this library's kernels launched per stan_cuda_glm_launch call for this data. */

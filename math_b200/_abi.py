@@ -151,6 +151,7 @@ PROTOTYPES = {
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "stan_cuda_glm_launch_ordered": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "stan_cuda_glm_launch_categorical": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "stan_cuda_glm_launch_noalloc": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "stan_cuda_allreduce": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p]),
     "stan_cuda_data_launches_per_eval": (C.c_int, [C.c_void_p]),
     "stan_cuda_data_y_range": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

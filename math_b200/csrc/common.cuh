@@ -69,6 +69,7 @@ struct Workspace {   // per (host thread, device) or per data handle: one launch
   double* scratch = nullptr;  // [max_grid][kpad_cap + 4] per-CTA partials
   unsigned int* ticket = nullptr;
   size_t scratch_doubles = 0;
+  bool fixed = false;  // a view of memory that must never be reallocated (stan_cuda_glm_launch_noalloc): reserve fails instead
 };
 int workspace_reserve(Workspace* w, int device, size_t doubles);
 void workspace_free(Workspace* w);

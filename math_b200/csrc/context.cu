@@ -169,6 +169,9 @@ int ThreadDev::reserve_y(size_t doubles) {
 
 int workspace_reserve(Workspace* w, int device, size_t doubles) {
   if (w->device == device && w->scratch && doubles <= w->scratch_doubles) return STAN_CUDA_OK;
+  if (w->fixed)
+    return fail(STAN_CUDA_ERR_ARG, "this problem needs " + std::to_string(doubles) + " doubles of reduction scratch, the fixed "
+                                   "scratch of the no-allocation entry point holds " + std::to_string(w->scratch_doubles));
   SC_CUDA(cudaSetDevice(device));
   if (w->scratch && w->device == device) {
     SC_CUDA(cudaDeviceSynchronize());

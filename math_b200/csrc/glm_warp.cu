@@ -631,3 +631,92 @@ int launch_glm_warp_batch(const stan_cuda_data* const* ds, const LaunchIO* ios, 
 }
 
 }  // namespace stancuda
+
+// =============================================================================================
+// stan_cuda_glm_launch_noalloc -- the fused GLM evaluation for callers that cannot allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.
+//
+// The kernel is the same glm_warp_kernel.  What differs is where its reduction scratch lives: the per-CTA
+// partials, the group sums and the ticket words of finish_reduction sit in the two file-scope __device__ arrays
+// below instead of a cudaMalloc'ed Workspace.  Every GPU that loads the library holds the arrays (1.27 MiB + 256 B)
+// until the process exits.  In host code the array NAMES are host-side stand-ins, not device addresses: the
+// addresses the kernel receives are resolved with cudaGetSymbolAddress, once per device, with that device current.
+// ALL calls on a device share the arrays, which keep the previous call's contents: the kernel overwrites every
+// partial it later reads, the ticket words (which must start at zero) are cleared on the stream in front of
+// every launch; two calls that OVERLAP on one GPU (different streams, concurrent host threads) race on the
+// scratch -- serialise them.
+// =============================================================================================
+namespace stancuda {
+
+constexpr size_t kNoAllocScratchDoubles = size_t(320) * 520;  // (296 CTAs + 18 group sums) x (k_pad 512 + 4) and the 2-double tail
+constexpr size_t kNoAllocTicketWords = 64;
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocScratchDoubles];
+static __device__ __align__(256) unsigned int g_noalloc_ticket[kNoAllocTicketWords];
+
+struct NoAllocDevice {
+  bool ready = false;
+  double* scratch = nullptr;       // device address of g_noalloc_scratch on this device
+  unsigned int* ticket = nullptr;  // device address of g_noalloc_ticket on this device
+};
+static std::mutex g_noalloc_mu;
+static NoAllocDevice g_noalloc_dev[64];
+
+// once per device, with that device current
+static int noalloc_setup(int device, NoAllocDevice** out) {
+  if (device < 0 || device >= 64) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  NoAllocDevice& nd = g_noalloc_dev[device];
+  if (!nd.ready) {
+    SC_CUDA(cudaSetDevice(device));
+    void* ps = nullptr;
+    void* pt = nullptr;
+    SC_CUDA(cudaGetSymbolAddress(&ps, g_noalloc_scratch));
+    SC_CUDA(cudaGetSymbolAddress(&pt, g_noalloc_ticket));
+    if (!ps || !pt) return fail(STAN_CUDA_ERR_CUDA, "stan_cuda_glm_launch_noalloc: cudaGetSymbolAddress returned null");
+    nd.scratch = static_cast<double*>(ps);
+    nd.ticket = static_cast<unsigned int*>(pt);
+    nd.ready = true;
+  }
+  *out = &nd;
+  return STAN_CUDA_OK;
+}
+
+}  // namespace stancuda
+
+extern "C" int stan_cuda_glm_launch_noalloc(stan_cuda_data_t d, uint32_t flags, const double* d_params, double* d_result,
+                                            void* stream) {
+  using namespace stancuda;
+  if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: null argument");
+  if (d->family > STAN_CUDA_NORMAL_ID)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: bernoulli_logit, poisson_log and normal_id only");
+  if (d->t.layout != kLayoutWarp)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: the data block was created for another kernel variant");
+  if (flags & STAN_CUDA_FUSED_ALLREDUCE)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: no collective on this entry point");
+  // largest problem the fixed scratch serves: (CTAs + reduction groups) x (k_pad + 4) + 2 doubles
+  const int64_t sms = sm_count(d->device);
+  int64_t grid = sms * 2 < d->t.tiles ? sms * 2 : d->t.tiles;
+  int64_t gs = 1;
+  while (gs * gs < grid) ++gs;
+  const size_t need = size_t(grid + (grid + gs - 1) / gs) * (size_t(d->t.kpad) + 4) + 2;
+  if (need > kNoAllocScratchDoubles)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: the problem needs " + std::to_string(need) +
+                                       " doubles of reduction scratch, the fixed scratch holds " +
+                                       std::to_string(kNoAllocScratchDoubles) + " (k_pad <= 512 on at most 160 SMs)");
+  NoAllocDevice* nd = nullptr;
+  SC_TRY(noalloc_setup(d->device, &nd));
+  SC_CUDA(cudaSetDevice(d->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // the ticket words must start at zero; a launch leaves them at zero, but the array is shared and outlives aborted runs
+  SC_CUDA(cudaMemsetAsync(nd->ticket, 0, kNoAllocTicketWords * sizeof(unsigned int), st));
+  Workspace view;  // not owned: never freed, never grown
+  view.device = d->device;
+  view.scratch = nd->scratch;
+  view.ticket = nd->ticket;
+  view.scratch_doubles = kNoAllocScratchDoubles;
+  view.fixed = true;
+  LaunchIO io{flags, d_params, nullptr, nullptr, d_result, nullptr, nullptr};
+  return launch_glm_warp(d, io, &view, st);
+}
+
