@@ -623,6 +623,9 @@ int glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int*
   }
   if (bad) return STAN_CUDA_BAD_OUTCOME;
 
+  if (!ents[0]->shards[0].d->colblocks.empty())
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval_batch: k <= 512 only (wider matrices run as several launches per item: "
+                                   "use stan_cuda_glm_eval)");
   const int kpad = ents[0]->shards[0].d->t.kpad;
   const size_t np = size_t(kpad) + 2, nr = size_t(kpad) + 4;
   const size_t npa = (np + 1) & ~size_t(1), nra = (nr + 1) & ~size_t(1);

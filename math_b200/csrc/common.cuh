@@ -91,6 +91,10 @@ struct stan_cuda_data {
   int hist_len = 0;
   size_t bytes = 0;
   stancuda::Workspace ws;  // used by the device-level API (stan_cuda_glm_launch)
+  // k > 512: the columns are split into blocks of kColBlock, each a complete data block of its own (x tiled for
+  // the warp kernel; the last one carries the real family, the others kFamilyLinearBlock).  This head block then
+  // holds no x of its own; its t is the last block's tiling with kpad = the sum over the blocks.
+  std::vector<stan_cuda_data*> colblocks;
 };
 
 namespace stancuda {
@@ -128,6 +132,11 @@ struct LaunchIO {
   double* d_dx = nullptr;
   int64_t ld_dx = 0;
 };
+// Internal pseudo-family of the column-block path (k > 512, glm_warp.cu launch_glm_colblocks): a block of columns
+// contributes eta_b = X_b beta_b to a per-row carry vector, or dbeta_b = X_b^T d from a per-row d vector.  Never
+// seen at the C ABI.
+constexpr int kFamilyLinearBlock = 6;
+constexpr int kColBlock = 512;               // columns per block: the widest tile of the warp kernel (C = 32, kc = 16)
 constexpr int kMaxClasses = 16;              // categorical_logit: classes on the device path
 constexpr int kMaxClassWeights = 4096;       // categorical_logit: classes * k_pad (weights live in shared memory)
 constexpr int kMaxCuts = 256;                // ordered_logistic: per-warp bins live in shared memory
@@ -137,6 +146,7 @@ constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sig
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+int launch_glm_colblocks(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 // width of the result block (and of every partial) of one launch

@@ -262,11 +262,50 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
   return STAN_CUDA_OK;
 }
 
+static thread_local bool tl_block_of_wider_matrix = false;  // set while the column blocks of a k > 512 matrix are built
+
 int make_data_block(int device, int family, int64_t n_rows, int64_t k, const double* x, int64_t ldx,
                     int x_row_major, const void* y, int y_is_double, int64_t row0, cudaStream_t stream,
                     stan_cuda_data** out) {
   if (n_rows <= 0 || k < 0 || (!x && k > 0) || !y) return fail(STAN_CUDA_ERR_ARG, "data block: bad shape or null pointer");
-  if (family < 0 || family > STAN_CUDA_CATEGORICAL_LOGIT) return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
+  if (family < 0 || (family > STAN_CUDA_CATEGORICAL_LOGIT && family != kFamilyLinearBlock))
+    return fail(STAN_CUDA_ERR_ARG, "data block: unknown family");
+  if (k > kColBlock && family != STAN_CUDA_CATEGORICAL_LOGIT && family != kFamilyLinearBlock) {
+    // wider than one warp tile: column blocks (glm_warp.cu, launch_glm_colblocks).  Only the last block is padded,
+    // so the concatenated parameter / gradient layout is [beta(k), zeros] like that of a single block.
+    const int64_t B = (k + kColBlock - 1) / kColBlock;
+    if (B > 4096) return fail(STAN_CUDA_ERR_ARG, "data block: more than 2097152 columns");
+    stan_cuda_data* head = new stan_cuda_data();
+    head->device = device;
+    head->family = family;
+    head->n = n_rows;
+    head->k = k;
+    head->y_is_double = y_is_double;
+    for (int64_t b = 0; b < B; ++b) {
+      const int64_t c0 = b * kColBlock;
+      const int64_t kb = (k - c0 < kColBlock) ? (k - c0) : int64_t(kColBlock);
+      const double* xb = x_row_major ? x + c0 : x + c0 * ldx;
+      stan_cuda_data* sub = nullptr;
+      tl_block_of_wider_matrix = true;  // every block on the warp kernel's layout, whatever variant is selected
+      const int rc = make_data_block(device, b == B - 1 ? family : kFamilyLinearBlock, n_rows, kb, xb, ldx, x_row_major, y,
+                                     y_is_double, row0, stream, &sub);
+      tl_block_of_wider_matrix = false;
+      if (rc < 0) {
+        free_data_block(head);
+        return rc;
+      }
+      head->colblocks.push_back(sub);
+      head->bytes += sub->bytes;
+    }
+    const stan_cuda_data* last = head->colblocks.back();
+    head->t = last->t;
+    head->t.kpad = int((B - 1) * kColBlock) + last->t.kpad;
+    head->lgamma_sum = last->lgamma_sum;
+    head->y_min = last->y_min;
+    head->y_max = last->y_max;
+    *out = head;
+    return STAN_CUDA_OK;
+  }
   stan_cuda_data* d = new stan_cuda_data();
   d->device = device;
   d->family = family;
@@ -275,7 +314,7 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
   d->y_is_double = y_is_double;
   // neg_binomial_2_log and ordered_logistic exist on the warp kernel only; categorical_logit has its own two
   // kernels: FP64 tensor-core (fragment layout, k <= 256) or vector (warp layout)
-  int force = family >= STAN_CUDA_NEG_BINOMIAL_2_LOG ? kLayoutWarp : -1;
+  int force = (family >= STAN_CUDA_NEG_BINOMIAL_2_LOG || tl_block_of_wider_matrix) ? kLayoutWarp : -1;
   if (family == STAN_CUDA_CATEGORICAL_LOGIT && tuning().cat_mma && k <= 256) force = kLayoutMma;
   if (!choose_tiling(n_rows, k, 0, &d->t, force)) {
     delete d;
@@ -300,6 +339,8 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
 
 void free_data_block(stan_cuda_data* d) {
   if (!d) return;
+  for (stan_cuda_data* sub : d->colblocks) free_data_block(sub);
+  d->colblocks.clear();
   cudaSetDevice(d->device);
   if (d->x) cudaFree(d->x);
   if (d->y) cudaFree(d->y);

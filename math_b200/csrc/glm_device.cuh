@@ -468,6 +468,8 @@ __device__ __forceinline__ void finish_reduction(const GlmKernelParams& p, int t
       if (p.flags & STAN_CUDA_LP_CONST) lp -= p.lgamma_sum;  // :102-108
       if (p.flags & STAN_CUDA_LP_MAIN) lp += A0;             // :109-112
       witness = A1;  // poisson_log_glm_lpmf.hpp:97 tests sum(theta_derivative)
+    } else if (FAMILY == kFamilyLinearBlock) {
+      witness = 0.0;  // a column block of the k > 512 path: no log-density of its own
     } else if (FAMILY == STAN_CUDA_CATEGORICAL_LOGIT) {
       if (p.flags & STAN_CUDA_LP_MAIN) lp = A0;
       witness = A0;  // categorical_logit_glm_lpmf.hpp:109 tests logp

@@ -412,6 +412,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
 }
 
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
+  if (!d->colblocks.empty()) return launch_glm_colblocks(d, io, ws, stream);  // k > 512
   const Tiling& t = d->t;
   if (d->family == STAN_CUDA_CATEGORICAL_LOGIT)
     return t.layout == kLayoutMma ? launch_glm_categorical_mma(d, io, ws, stream) : launch_glm_categorical(d, io, ws, stream);

@@ -140,6 +140,17 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
   // the row (`own`) adds the terms to its accumulators and writes the per-row outputs.  `slot` is the
   // row's slot in the d/dcuts bins, `u` the PAIR role (0: tile A, 1: tile B; always 0 otherwise).
   auto row_terms = [&](double eta, double yv, int64_t row, bool valid, bool own, int slot, int u) -> double {
+    if (FAMILY == kFamilyLinearBlock) {
+      // column-block path (k > 512): this block's share of the linear predictor goes into the per-row carry
+      // (row_dsigma = carry out, alpha_vec | alpha0 = carry in), or a given per-row d (sigma_vec) drives X_b^T d
+      double dd = 0.0;
+      if (valid) {
+        if (own && p.row_dsigma) p.row_dsigma[row] = eta + (p.alpha_vec ? p.alpha_vec[row] : alpha0);
+        if (p.sigma_vec) dd = p.sigma_vec[row];
+        if (own) a1 += dd;
+      }
+      return dd;
+    }
     double alpha = alpha0, inv_sigma = inv_sigma0, sigma_row = sigma0, log_sigma_row = log_sigma0;
     if (ROWIO && valid) {
       if (p.alpha_vec) alpha = p.alpha_vec[row];
@@ -152,11 +163,13 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
     RowTerms o;
     if (FAMILY == STAN_CUDA_ORDERED_LOGISTIC) {
       const int c = valid ? int(yv) : 1;  // 1 <= c <= ncuts + 1 was checked from the range of y cached at fill
+      if (ROWIO && p.alpha_vec) eta += alpha;  // column-block path: the other blocks' share of the location
       o = ordered_row_epilogue(eta, c, ncuts + 1, ord_tab);
       if (valid && own) {
         a0 += o.t0;
         a1 += o.d;
         a2 += eta;  // ordered_logistic_glm_lpmf.hpp:119: finiteness of sum(location)
+        if (ROWIO && p.row_dalpha) p.row_dalpha[row] = o.d;
       }
       if ((p.flags & STAN_CUDA_NEED_DCUTS) && ord_private) {
         // d/dcuts (:192-200), few classes: every row slot of the tile owns a private row of bins
@@ -532,8 +545,11 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
       return (rowio || p.nb_rowfun) ? launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, true>(p, grid, smem, stream)
                    : launch_warp_inst<STAN_CUDA_NEG_BINOMIAL_2_LOG, false>(p, grid, smem, stream);
     case STAN_CUDA_ORDERED_LOGISTIC:
-      if (rowio) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic has no per-row operands");
-      return launch_warp_inst<STAN_CUDA_ORDERED_LOGISTIC, false>(p, grid, smem, stream);
+      // per-row operands of ordered_logistic exist only inside the column-block path (carry in, d out)
+      return rowio ? launch_warp_inst<STAN_CUDA_ORDERED_LOGISTIC, true>(p, grid, smem, stream)
+                   : launch_warp_inst<STAN_CUDA_ORDERED_LOGISTIC, false>(p, grid, smem, stream);
+    case kFamilyLinearBlock:
+      return launch_warp_inst<kFamilyLinearBlock, true>(p, grid, smem, stream);
   }
   return fail(STAN_CUDA_ERR_ARG, "launch_glm: unknown family");
 }
@@ -628,6 +644,107 @@ int launch_glm_warp_batch(const stan_cuda_data* const* ds, const LaunchIO* ios, 
     case STAN_CUDA_POISSON_LOG: return launch_warp_batch_family<STAN_CUDA_POISSON_LOG>(fullkc, pair, d_batch, grid, smem, stream);
     default: return launch_warp_batch_family<STAN_CUDA_NORMAL_ID>(fullkc, pair, d_batch, grid, smem, stream);
   }
+}
+
+// =============================================================================================
+// k > 512: column blocks.  The reference accepts any number of columns (bernoulli_logit_glm_lpmf.hpp:60-69 only
+// checks consistency); the fused kernel keeps a row's columns in one warp (<= 32 lanes x 16), so wider matrices
+// are split into blocks of kColBlock columns, each tiled like a matrix of its own:
+//   1. blocks 0 .. B-2 (kFamilyLinearBlock): carry[row] = X_b beta_b + carry[row]   (carry starts as alpha)
+//   2. block B-1 (the real family, per-row intercept = carry): log-density, d = dL/deta per row, dbeta_{B-1}
+//   3. blocks 0 .. B-2 again: dbeta_b = X_b^T d
+// Blocks 0 .. B-2 cross HBM twice, the last one once: (2 - 1/B) x the bytes of one read of X.  Every launch is the
+// same glm_warp_kernel with its fixed-order reductions, so results stay bit-reproducible.
+// =============================================================================================
+__global__ void colblock_split_params_kernel(const double* __restrict__ full, double* __restrict__ blocks, int nblocks,
+                                             int kpad_last, int ncuts, int alpha_to_first) {
+  // full = [beta(kpad_total), alpha, sigma, cuts(ncuts)];  blocks[b] = [beta_b(kpad_b), alpha_b, sigma, cuts] at stride
+  const int b = blockIdx.x;
+  const int kpad_total = (nblocks - 1) * kColBlock + kpad_last;
+  const int kpad_b = b == nblocks - 1 ? kpad_last : kColBlock;
+  const size_t stride = size_t(kColBlock) + 2 + ncuts;
+  double* dst = blocks + size_t(b) * stride;
+  for (int j = threadIdx.x; j < kpad_b; j += blockDim.x) dst[j] = full[size_t(b) * kColBlock + j];
+  if (threadIdx.x == 0) {
+    // the scalar intercept enters the carry chain at block 0; the last block then reads it from the carry vector
+    dst[kpad_b] = (alpha_to_first ? b == 0 : b == nblocks - 1) ? full[kpad_total] : 0.0;
+    dst[kpad_b + 1] = full[kpad_total + 1];
+  }
+  for (int j = threadIdx.x; j < ncuts; j += blockDim.x) dst[kpad_b + 2 + j] = full[kpad_total + 2 + j];
+}
+
+__global__ void colblock_gather_result_kernel(const double* __restrict__ blocks, double* __restrict__ result, int nblocks,
+                                              int kpad_last, int ncuts, int have_dbeta) {
+  // blocks[b] = [lp, sum d, a2, witness, dbeta_b(kpad_b), dcuts] at stride; result = [4][dbeta(kpad_total)][dcuts]
+  const int b = blockIdx.x;
+  const int kpad_total = (nblocks - 1) * kColBlock + kpad_last;
+  const int kpad_b = b == nblocks - 1 ? kpad_last : kColBlock;
+  const size_t stride = size_t(kColBlock) + 4 + ncuts;
+  const double* src = blocks + size_t(b) * stride;
+  for (int j = threadIdx.x; j < kpad_b; j += blockDim.x)
+    result[4 + size_t(b) * kColBlock + j] = (have_dbeta || b == nblocks - 1) ? src[4 + j] : 0.0;
+  if (b == nblocks - 1) {
+    if (threadIdx.x < 4) result[threadIdx.x] = src[threadIdx.x];
+    for (int j = threadIdx.x; j < ncuts; j += blockDim.x) result[4 + kpad_total + j] = src[4 + kpad_b + j];
+  }
+}
+
+int launch_glm_colblocks(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
+  const int B = int(d->colblocks.size());
+  if (B < 2) return fail(STAN_CUDA_ERR_STATE, "launch_glm: column-block data without blocks");
+  if (io.xchg || io.host_flag || io.h_params_inline)
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: k > 512 runs as several launches: no in-kernel all-reduce / inline parameters "
+                                   "(use stan_cuda_allreduce behind the launch)");
+  if (!io.d_params) return fail(STAN_CUDA_ERR_ARG, "launch_glm: no parameter block");
+  const stan_cuda_data* last = d->colblocks[size_t(B) - 1];
+  const int ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
+  if (ncuts < 0 || ncuts > kMaxCuts)
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
+  const int kpad_last = last->t.kpad;
+  const size_t np_stride = size_t(kColBlock) + 2 + ncuts, nr_stride = size_t(kColBlock) + 4 + ncuts;
+  const size_t rows_al = (size_t(d->n) + 1) & ~size_t(1);
+  // one allocation: [partials of the running launch | parameter blocks | result blocks | carry | d] (+ the 2-double
+  // tail neg_binomial_2_log uses); the sub-launches find their partials region already large enough
+  const size_t partials = size_t(2 * sm_count(d->device) + 64) * nr_stride + 2;
+  const size_t extras = size_t(B) * (np_stride + nr_stride) + 2 * rows_al + 8;
+  SC_CUDA(cudaSetDevice(d->device));
+  SC_TRY(workspace_reserve(ws, d->device, partials + extras + 4));
+  double* base = ws->scratch + ((partials + 1) & ~size_t(1));
+  double* par = base;
+  double* res = par + size_t(B) * np_stride;
+  double* carry = res + size_t(B) * nr_stride;
+  double* drow = io.d_row_dalpha ? io.d_row_dalpha : carry + rows_al;
+
+  colblock_split_params_kernel<<<B, 256, 0, stream>>>(io.d_params, par, B, kpad_last, ncuts, io.d_alpha_vec ? 0 : 1);
+  SC_CUDA(cudaGetLastError());
+  // 1. carry chain over the leading blocks
+  for (int b = 0; b < B - 1; ++b) {
+    LaunchIO sub{0u, par + size_t(b) * np_stride, nullptr, nullptr, res + size_t(b) * nr_stride, nullptr, carry};
+    sub.d_alpha_vec = b == 0 ? io.d_alpha_vec : carry;
+    sub.shared_gpu = io.shared_gpu;
+    SC_TRY(launch_glm_warp(d->colblocks[size_t(b)], sub, ws, stream));
+  }
+  // 2. the family's own block: intercept per row = carry, d per row out
+  {
+    LaunchIO sub{io.flags, par + size_t(B - 1) * np_stride, carry, io.d_sigma_vec, res + size_t(B - 1) * nr_stride, drow,
+                 io.d_row_dsigma};
+    sub.ncuts = io.ncuts;
+    sub.d_y = io.d_y;
+    sub.y_lgamma_sum = io.y_lgamma_sum;
+    sub.shared_gpu = io.shared_gpu;
+    SC_TRY(launch_glm_warp(last, sub, ws, stream));
+  }
+  // 3. gradient of the leading blocks from d
+  const bool have_dbeta = (io.flags & STAN_CUDA_NEED_DBETA) != 0;
+  for (int b = 0; have_dbeta && b < B - 1; ++b) {
+    LaunchIO sub{0u, par + size_t(b) * np_stride, nullptr, drow, res + size_t(b) * nr_stride, nullptr, nullptr};
+    sub.shared_gpu = io.shared_gpu;
+    SC_TRY(launch_glm_warp(d->colblocks[size_t(b)], sub, ws, stream));
+  }
+  colblock_gather_result_kernel<<<B, 256, 0, stream>>>(res, io.d_result, B, kpad_last, ncuts, have_dbeta ? 1 : 0);
+  SC_CUDA(cudaGetLastError());
+  counters().launches.fetch_add(2, std::memory_order_relaxed);
+  return STAN_CUDA_OK;
 }
 
 }  // namespace stancuda

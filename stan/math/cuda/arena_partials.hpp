@@ -4,6 +4,8 @@
 
 #include <stan/math/cuda/marshal.hpp>
 #include <stan/math/rev/core/precomputed_gradients.hpp>
+#include <atomic>
+#include <cstdint>
 #include <vector>
 
 namespace stan {
@@ -30,6 +32,76 @@ inline void dump_var_array(const var* v, size_t n, vari** dst) {
     }
   });
 }
+
+/** smallest edge for which the adjoint scatter of chain() is spread over the TBB workers */
+constexpr size_t bulk_chain_min = size_t(1) << 17;
+
+/** true when the operand addresses of an edge are strictly ascending -- which proves that no vari occurs twice,
+ * so the adjoint updates of different elements never touch the same memory.  It is what a vector of parameters
+ * built element after element on the autodiff arena looks like; anything else keeps the serial loop. */
+inline bool strictly_ascending(vari* const* v, size_t n) {
+#ifdef STAN_THREADS
+  std::atomic<bool> ok(true);
+  for_each_chunk(n, [&](size_t begin, size_t end) {
+    bool mine = true;
+    for (size_t i = begin > 0 ? begin : 1; i < end; ++i) {
+      mine = mine && (reinterpret_cast<uintptr_t>(v[i - 1]) < reinterpret_cast<uintptr_t>(v[i]));
+    }
+    if (!mine) {
+      ok.store(false, std::memory_order_relaxed);
+    }
+  });
+  return ok.load();
+#else
+  (void)v;
+  (void)n;
+  return false;
+#endif
+}
+
+/**
+ * The reference's precomputed_gradients_vari (rev/core/precomputed_gradients.hpp:20-76) with the adjoint scatter of
+ * chain() (:71-75, one host thread over all N operands) run edge by edge over the TBB workers.  Same node layout,
+ * same arithmetic per operand (one multiply-add into each operand's adjoint, so the result is bit-identical to the
+ * serial loop); only edges whose operands are provably distinct (strictly ascending addresses) and large are spread,
+ * the others run the reference's loop.  Edges run one after the other: the same vari may sit in two edges.
+ */
+class bulk_gradients_vari : public precomputed_gradients_vari {
+ public:
+  bulk_gradients_vari(double val, size_t size, vari** varis, double* gradients, const size_t* edge_offsets,
+                      const bool* edge_parallel)
+      : precomputed_gradients_vari(val, size, varis, gradients) {
+    for (int e = 0; e < 6; ++e) {
+      off_[e] = edge_offsets[e];
+    }
+    for (int e = 0; e < 5; ++e) {
+      par_[e] = edge_parallel[e];
+    }
+  }
+  void chain() {
+    const double adj = adj_;
+    vari** varis = varis_;
+    const double* gradients = gradients_;
+    for (int e = 0; e < 5; ++e) {
+      const size_t b = off_[e], n = off_[e + 1] - off_[e];
+      if (par_[e]) {
+        for_each_chunk(n, [=](size_t begin, size_t end) {
+          for (size_t i = b + begin; i != b + end; ++i) {
+            varis[i]->adj_ += adj * gradients[i];
+          }
+        });
+      } else {
+        for (size_t i = b; i != b + n; ++i) {
+          varis[i]->adj_ += adj * gradients[i];
+        }
+      }
+    }
+  }
+
+ private:
+  size_t off_[6];
+  bool par_[5];
+};
 template <>
 struct operand_edge<std::vector<var>> {
   static size_t size(const std::vector<var>& v) { return v.size(); }
@@ -103,6 +175,15 @@ class arena_partials {
  private:
   double build(double value, std::true_type /*all arithmetic*/) const { return value; }
   var build(double value, std::false_type) const {
+    bool par[5];
+    bool any = false;
+    for (int e = 0; e < 5; ++e) {
+      par[e] = n_[e] >= bulk_chain_min && strictly_ascending(varis_ + off_[e], n_[e]);
+      any = any || par[e];
+    }
+    if (any) {  // N-element edges: the adjoint scatter of chain() runs over the TBB workers
+      return var(new bulk_gradients_vari(value, off_[5], varis_, partials_, off_, par));
+    }
     return var(new precomputed_gradients_vari(value, off_[5], varis_, partials_));
   }
   size_t n_[5];

@@ -146,7 +146,9 @@ TEST_P(CudaGlm, bernoulli_poisson_normal_match_reference_body) {
 INSTANTIATE_TEST_CASE_P(Shapes, CudaGlm,
                         ::testing::Values(std::make_pair(3, 2), std::make_pair(1, 1), std::make_pair(153, 71),
                                           std::make_pair(5000, 32), std::make_pair(20000, 128),
-                                          std::make_pair(3000, 256), std::make_pair(40, 0)));
+                                          std::make_pair(3000, 256), std::make_pair(40, 0),
+                                          // wider than one warp tile (k > 512): the column-block path
+                                          std::make_pair(300, 513), std::make_pair(800, 1100)));
 
 TEST(CudaGlmVariants, vector_alpha_vector_sigma_var_y) {
   Problem p = make_problem(153, 71, 7);
@@ -176,6 +178,19 @@ TEST(CudaGlmVariants, vector_alpha_vector_sigma_var_y) {
   Matrix<int, Dynamic, 1> y_eig = Eigen::Map<Matrix<int, Dynamic, 1>>(p.y_pois.data(), p.y_pois.size());
   var d = poisson_log_glm_lpmf(y_eig, p.x, alpha, beta);
   expect_rel(d.val(), c.val(), std::fabs(c.val()), "Eigen int y");
+  stan::math::recover_memory();
+}
+
+TEST(CudaGlmVariants, wide_matrix_vector_alpha_vector_sigma_var_y) {
+  // k > 512 with per-row operands: the carry chain starts from the intercept vector, d comes back per row
+  Problem p = make_problem(211, 600, 9);
+  vector_v beta = to_v(p.beta), alpha_v = to_v(p.alpha_vec), sigma_v = to_v(p.sigma_vec), y_v = to_v(p.y_norm);
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("wide bernoulli vector alpha", bernoulli_logit_glm_lpmf(p.y_bern, p.x, alpha_v, beta),
+                   bernoulli_logit_glm_lpmf_reference_cpu(p.y_bern, p.x, alpha_v, beta), adj(beta), adj(alpha_v));
+  STAN_CUDA_PARITY("wide normal all vectors + var y", normal_id_glm_lpdf(y_v, p.x, alpha_v, beta, sigma_v),
+                   normal_id_glm_lpdf_reference_cpu(y_v, p.x, alpha_v, beta, sigma_v), adj(beta), adj(alpha_v),
+                   adj(sigma_v), adj(y_v));
   stan::math::recover_memory();
 }
 
@@ -343,6 +358,29 @@ TEST(CudaNormalLpdf, vectorised_matches_reference_loop) {
   // known answers of test/prob/normal/normal_test.hpp:11-40 through the vectorised entry
   std::vector<double> y1{-3.5}, m1{1.9}, s1{7.2};
   EXPECT_NEAR(-3.174269559226682080322, normal_lpdf(y1, m1, s1), 1e-14);
+  stan::math::recover_memory();
+}
+
+TEST(CudaNormalLpdf, bulk_adjoint_scatter_matches_the_reference_node) {
+  // N above the threshold of the parallel chain() (stan/math/cuda/arena_partials.hpp, bulk_gradients_vari): operands
+  // built one after the other (strictly ascending addresses: scattered in parallel), the same vector used for two
+  // arguments (edges run one after the other), and a vector that repeats ONE var (not ascending: serial loop)
+  const int n = 300001;
+  Problem p = make_problem(n, 1, 6);
+  vector_v mu = to_v(0.1 * p.y_norm), y_v = to_v(p.y_norm);
+  var sigma = 1.3;
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("normal_lpdf bulk", normal_lpdf(p.y_norm, mu, sigma), normal_lpdf_reference_cpu(p.y_norm, mu, sigma),
+                   adj(mu), VectorXd::Constant(1, sigma.adj()));
+  vector_v pos = to_v(p.sigma_vec);  // positive: usable as location and as scale
+  STAN_CUDA_PARITY("normal_lpdf bulk, one vector in two edges", normal_lpdf(y_v, pos, pos), normal_lpdf_reference_cpu(y_v, pos, pos),
+                   adj(pos), adj(y_v));
+  var m = 0.25;
+  vector_v repeated(n);
+  for (int i = 0; i < n; ++i) repeated[i] = m;
+  STAN_CUDA_PARITY("normal_lpdf one var repeated", normal_lpdf(p.y_norm, repeated, sigma),
+                   normal_lpdf_reference_cpu(p.y_norm, repeated, sigma), VectorXd::Constant(1, m.adj()),
+                   VectorXd::Constant(1, sigma.adj()));
   stan::math::recover_memory();
 }
 

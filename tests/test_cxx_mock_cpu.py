@@ -69,7 +69,7 @@ def test_arena_node_equals_operands_and_partials(mock_env):
     exe = os.path.join(CXX_DIR, "host_phases")
     if not os.path.exists(exe):
         pytest.skip("host_phases not built (test/Makefile needs /root/reference)")
-    for n in ("1000", "70001"):
+    for n in ("1000", "70001", "300001"):   # the last one is above the threshold of the parallel chain()
         r = subprocess.run([exe, n, "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300, env=mock_env)
         assert r.returncode == 0, r.stdout
         out = json.loads(r.stdout)

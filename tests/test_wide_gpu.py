@@ -1,0 +1,107 @@
+"""GPU parity tests of design matrices wider than one warp tile (k > 512): the column-block path of
+csrc/glm_warp.cu (launch_glm_colblocks).  The reference accepts any number of columns
+(stan/math/prim/mat/prob/bernoulli_logit_glm_lpmf.hpp:60-69 only checks consistency); round 1 raised
+std::system_error beyond 512."""
+import numpy as np
+import pytest
+
+from math_b200 import _abi
+from tests.helpers import assert_close, check_glm_result, check_ord_result, synth_glm, synth_ordered
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def glm():
+    from math_b200 import glm as g
+    from math_b200._lib import lib
+    g.init(1)
+    lib().stan_cuda_set_kernel(1)
+    yield g
+    g.cache_clear()
+
+
+@pytest.fixture(scope="module")
+def L():
+    from oracle import loader
+    return loader
+
+
+@pytest.mark.parametrize("k", [513, 1000, 4096])
+@pytest.mark.parametrize("family", ["bernoulli_logit", "poisson_log", "normal_id"])
+def test_wide_hot_path_families_match_the_oracle(glm, L, family, k):
+    n = 3001 if k < 4096 else 1500
+    s = synth_glm(family, n, k, seed=k)
+    s["beta"] = s["beta"] * (8.0 / np.sqrt(k))        # keep the linear predictor O(1)
+    ref = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"])
+    got = glm.glm_eval(family, s["y"], s["x"], s["alpha"], s["beta"], s["sigma"])
+    assert got["rc"] == 0
+    check_glm_result(got, ref, "%s %dx%d" % (family, n, k))
+    again = glm.glm_eval(family, got["_keep"][1], got["_keep"][0], s["alpha"], s["beta"], s["sigma"])
+    assert again["lp"] == got["lp"] and np.array_equal(again["dbeta"], got["dbeta"])   # bit-reproducible
+    # row-major x takes the same path
+    xr = np.ascontiguousarray(s["x"])
+    got = glm.glm_eval(family, s["y"], xr, s["alpha"], s["beta"], s["sigma"])
+    check_glm_result(got, ref, "%s %dx%d row-major" % (family, n, k))
+    glm.cache_clear()
+
+
+def test_wide_per_row_operands(glm, L):
+    n, k = 2003, 700
+    s = synth_glm("normal_id", n, k, seed=5)
+    s["beta"] = s["beta"] * 0.3
+    rng = np.random.default_rng(2)
+    alpha = 0.3 + 0.05 * rng.standard_normal(n)
+    sigma = 1.0 + 0.2 * rng.random(n)
+    ref = L.oracle_glm("normal_id", s["x"], s["y"], alpha, s["beta"], sigma, need_dy=True)
+    got = glm.glm_eval("normal_id", s["y"], s["x"], alpha, s["beta"], sigma, need_dy=True)
+    check_glm_result(got, ref, "wide normal_id vector alpha / sigma / dy")
+    sp = synth_glm("poisson_log", n, k, seed=6)
+    sp["beta"] = sp["beta"] * 0.3
+    ref = L.oracle_glm("poisson_log", sp["x"], sp["y"], alpha, sp["beta"])
+    got = glm.glm_eval("poisson_log", sp["y"], sp["x"], alpha, sp["beta"])
+    check_glm_result(got, ref, "wide poisson_log vector alpha")
+    glm.cache_clear()
+
+
+def test_wide_widened_families(glm, L):
+    n, k = 2501, 600
+    s = synth_glm("neg_binomial_2_log", n, k, seed=7)
+    s["beta"] = s["beta"] * 0.3
+    ref = L.oracle_glm("neg_binomial_2_log", s["x"], s["y"], s["alpha"], s["beta"], s["sigma"])
+    got = glm.glm_eval("neg_binomial_2_log", s["y"], s["x"], s["alpha"], s["beta"], s["sigma"])
+    check_glm_result(got, ref, "wide neg_binomial_2_log")
+    so = synth_ordered(n, 777, 5, seed=8)
+    flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+    got = glm.ordered_logistic_glm_eval(so["y"], so["x"], so["beta"], so["cuts"], flags)
+    check_ord_result(got, L.oracle_ordered_logistic_glm(so["x"], so["y"], so["beta"], so["cuts"]), "wide ordered_logistic")
+    glm.cache_clear()
+
+
+def test_wide_device_level_launch_and_y_per_call(glm, L):
+    import torch
+    n, k = 2777, 1030
+    s = synth_glm("poisson_log", n, k, seed=9)
+    s["beta"] = s["beta"] * 0.25
+    ref = L.oracle_glm("poisson_log", s["x"], s["y"], s["alpha"], s["beta"])
+    data = glm.GlmData("poisson_log", s["x"], s["y"])
+    try:
+        assert data.kpad >= k and data.params_len == data.kpad + 2
+        params = np.zeros(data.params_len)
+        params[:k], params[data.kpad], params[data.kpad + 1] = s["beta"], s["alpha"][0], 1.0
+        d_params = torch.from_numpy(params).cuda()
+        d_result = torch.zeros(data.result_len, dtype=torch.float64, device="cuda")
+        stream = torch.cuda.Stream()
+        data.launch(glm.glm_flags(_abi.POISSON_LOG, False), d_params.data_ptr(), d_result.data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        r = d_result.cpu().numpy()
+        assert_close(r[0], ref["lp"], "wide device-level lp")
+        assert_close(r[4:4 + k], ref["dbeta"], "wide device-level dbeta")
+        assert_close(r[1], ref["dalpha"][0], "wide device-level dalpha")
+        assert not np.any(r[4 + k:])                 # the padding columns of the last block carry zeros
+    finally:
+        data.close()
+    y2 = np.random.default_rng(1).permutation(s["y"])
+    got = glm.glm_eval("poisson_log", y2, s["x"], s["alpha"], s["beta"], y_per_call=True)
+    check_glm_result(got, L.oracle_glm("poisson_log", s["x"], y2, s["alpha"], s["beta"]), "wide y_per_call")
+    glm.cache_clear()

@@ -12,7 +12,7 @@ for tool in memcheck racecheck synccheck; do
   log="$OUT/${tool}_g${NDEV}.log"
   extra=""
   [ "$tool" = racecheck ] && extra="--racecheck-report all"
-  timeout 1500 "$CS" --tool "$tool" $extra --print-limit 40 --launch-timeout 300 \
+  timeout 700 "$CS" --tool "$tool" $extra --print-limit 40 --launch-timeout 300 \
       python tools/sanitize_cases.py "$NDEV" all > "$log" 2>&1
   code=$?
   echo "== $tool g$NDEV exit $code" | tee -a "$OUT/summary_g${NDEV}.txt"
