@@ -37,6 +37,7 @@ struct GlmKernelParams {
   int ncls, cat_groups;   // categorical_logit: classes; class groups of the gradient phase (glm_categorical.cu)
   int pair;               // warp kernel: two tiles per iteration (glm_warp.cu, PAIR)
   int ord_private;        // ordered_logistic: d/dcuts bins private to each row slot of the tile ([ncuts][R] in shared memory)
+  int pdl;                // launched with programmatic stream serialisation: see glm_warp.cu (early start of the next evaluation)
   // low-latency host path: parameters by value, completion flag in mapped host memory
   int inline_n;                        // > 0: read the parameter block from inline_params
   unsigned long long* host_flag;       // non-null: store host_seq there after the result block

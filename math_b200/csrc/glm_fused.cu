@@ -361,6 +361,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
   p->ord_private = 0;
   p->pair = 0;
+  p->pdl = 0;
   p->ncls = 0;
   p->cat_groups = 1;
   if (p->ncuts < 0 || p->ncuts > kMaxCuts) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");

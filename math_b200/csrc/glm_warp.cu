@@ -84,6 +84,12 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
     ntl = (p.tiles - int(blockIdx.x) + grid - 1) / grid;
   }
 
+  // Programmatic dependent launch (p.pdl): the NEXT evaluation on this stream may start while this one is still in
+  // its reduction / exchange tail.  Nothing a GLM kernel writes (per-CTA partials, tickets, result block, exchange
+  // slots) is touched before the griddepcontrol.wait further down, and everything it reads before that point (X, y,
+  // the parameter block) is never written by a GLM kernel -- so the tile loop of evaluation n + 1 overlaps the tail of
+  // evaluation n.  Kernels with per-row outputs (ROWIO, the column-block chain) are launched without the attribute.
+  if (p.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   PHASE_STAMP(0);
   if (tid == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -352,6 +358,8 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
     }
   }
   consumer_sync();
+  // first write to memory shared with the previous evaluation: wait until that grid has completed and flushed
+  if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
   double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
   for (int c = tid; c < cols; c += NT) {
     double sum = 0.0;
@@ -413,7 +421,21 @@ static int launch_warp_inst2(const GlmKernelParams& p, int grid, size_t smem, cu
     SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     configured[dev].store(smem, std::memory_order_relaxed);
   }
-  kern<<<grid, kWarpThreads, smem, stream>>>(p);
+  if (p.pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(unsigned(grid), 1, 1);
+    cfg.blockDim = dim3(kWarpThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SC_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+  } else {
+    kern<<<grid, kWarpThreads, smem, stream>>>(p);
+  }
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
@@ -513,6 +535,21 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
     if (g < 8) g = 8;
     if (g < grid64) grid64 = g;
   }
+  // Programmatic dependent launch for the plain instantiations of the three hot-path families (no per-row operands,
+  // not a column block, not next to other shards' launches).  A full-width grid then leaves `slack` CTA slots free:
+  // the previous evaluation's last CTA may still sit in its exchange when this grid starts, and with a static tile
+  // schedule a CTA that starts late finishes late.  STAN_CUDA_PDL=0 switches it off (A/B).
+  static const int pdl_on = [] {
+    const char* v = getenv("STAN_CUDA_PDL");
+    return v ? atoi(v) : 1;
+  }();
+  static const int pdl_slack = [] {
+    const char* v = getenv("STAN_CUDA_PDL_SLACK");
+    return v ? atoi(v) : 1;
+  }();
+  const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
+  const bool pdl = pdl_on != 0 && !rowio && d->family <= STAN_CUDA_NORMAL_ID && !io.shared_gpu && !ws->fixed;
+  if (pdl && grid64 == int64_t(sms) * ctas_per_sm && grid64 > pdl_slack + 8) grid64 -= pdl_slack;
   const int grid = int(grid64);
   int group_size = 1;
   while (group_size * group_size < grid) ++group_size;
@@ -528,7 +565,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   p.blocked = tuning().blocked;
   p.ord_private = ord_private_bins(t, ncuts) ? 1 : 0;
   p.pair = pair_mode(t) && stages >= 3 ? 1 : 0;
-  const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
+  p.pdl = pdl ? 1 : 0;
   switch (d->family) {
     case STAN_CUDA_BERNOULLI_LOGIT:
       return rowio ? launch_warp_inst<STAN_CUDA_BERNOULLI_LOGIT, true>(p, grid, smem, stream)

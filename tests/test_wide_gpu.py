@@ -33,16 +33,22 @@ def test_wide_hot_path_families_match_the_oracle(glm, L, family, k):
     n = 3001 if k < 4096 else 1500
     s = synth_glm(family, n, k, seed=k)
     s["beta"] = s["beta"] * (8.0 / np.sqrt(k))        # keep the linear predictor O(1)
-    ref = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"])
+    # The checker is the compiled reference where it exists (it travels to the GPU box): at k = 4096 the plain-C
+    # port's naive sums are themselves 1.6e-10 away from the exact gradient on its smallest components (measured
+    # against long double: reference 1.2e-11, port 1.6e-10), so the port is held to 1e-9 there.
+    if L.have_ref():
+        ref, rtol = L.ref_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"]), 1e-10
+    else:
+        ref, rtol = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"], s["sigma"]), (1e-10 if k < 4096 else 1e-9)
     got = glm.glm_eval(family, s["y"], s["x"], s["alpha"], s["beta"], s["sigma"])
     assert got["rc"] == 0
-    check_glm_result(got, ref, "%s %dx%d" % (family, n, k))
+    check_glm_result(got, ref, "%s %dx%d" % (family, n, k), rtol)
     again = glm.glm_eval(family, got["_keep"][1], got["_keep"][0], s["alpha"], s["beta"], s["sigma"])
     assert again["lp"] == got["lp"] and np.array_equal(again["dbeta"], got["dbeta"])   # bit-reproducible
     # row-major x takes the same path
     xr = np.ascontiguousarray(s["x"])
     got = glm.glm_eval(family, s["y"], xr, s["alpha"], s["beta"], s["sigma"])
-    check_glm_result(got, ref, "%s %dx%d row-major" % (family, n, k))
+    check_glm_result(got, ref, "%s %dx%d row-major" % (family, n, k), rtol)
     glm.cache_clear()
 
 
