@@ -152,7 +152,10 @@ typedef struct stan_cuda_glm_args {
    * outcome the wrapper broadcasts into a temporary.  The cache is then keyed on x ALONE and y travels to the
    * device with every call (its range and sum lgamma(y + 1) are recomputed per call), so x is never refilled. */
   int32_t y_per_call;
-  int32_t reserved0;
+  /* 1: x is not immutable data either (a var design matrix whose values the wrapper gathered into a temporary):
+   * nothing is looked up by address or content; x (and y) are uploaded and re-tiled on every call into device
+   * buffers the calling thread reuses from call to call. */
+  int32_t x_per_call;
   /* var x (bernoulli_logit_glm_lpmf.hpp:125-128, poisson_log_glm_lpmf.hpp:119-122,
    * normal_id_glm_lpdf.hpp:121-124): with STAN_CUDA_NEED_DX the kernel also streams out
    * d/dx[i][j] = d_i * beta_j, column-major n x k with leading dimension lddx (>= n), host memory. */

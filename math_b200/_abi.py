@@ -53,7 +53,7 @@ class GlmArgs(C.Structure):
         ("dcuts", C.c_void_p),
         ("n_classes", C.c_int64),
         ("y_per_call", C.c_int32),
-        ("reserved0", C.c_int32),
+        ("x_per_call", C.c_int32),
         ("dx", C.c_void_p),
         ("lddx", C.c_int64),
     ]

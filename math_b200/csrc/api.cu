@@ -207,6 +207,52 @@ static std::vector<int> pick_devices(int64_t n, int64_t k) {
 }
 
 static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* out) {
+  if (a->x_per_call) {
+    // var x: nothing to recognise -- the calling thread keeps one set of device buffers per (shape, family) and
+    // refills it on every call (upload + re-tiling; no cudaMalloc after the first call of that shape)
+    static thread_local char tl_thread_tag;
+    const int64_t bits = int64_t(a->family) * 8 + a->x_row_major * 2 + a->y_is_double + 64 * tuning().layout + 256 * tuning().cat_mma;
+    const Key key(4, uintptr_t(&tl_thread_tag), uintptr_t(tl_scope.active ? tl_scope.device + 1 : 0), a->n, a->k, a->ldx, bits);
+    std::shared_ptr<Entry> e;
+    {
+      std::lock_guard<std::mutex> lk(g_cache_mu);
+      auto it = g_cache.find(key);
+      if (it != g_cache.end()) {
+        e = it->second;
+        e->last_use = ++g_cache_tick;
+      }
+    }
+    if (e) {
+      for (Shard& sh : e->shards) {
+        ThreadDev* td;
+        SC_TRY(thread_dev(sh.d->device, &td));
+        SC_TRY(refill_data_block(sh.d, a->x, a->ldx, a->x_row_major, a->y, sh.row0, td->stream));
+      }
+      *out = e;
+      return STAN_CUDA_OK;
+    }
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    make_room_locked(a->n * ((a->k + 15) / 16 * 16 + 1) * int64_t(sizeof(double)));
+    e = std::make_shared<Entry>();
+    const std::vector<int> devs = pick_devices(a->n, a->k);
+    const int64_t G = int64_t(devs.size()), per = (a->n + G - 1) / G;
+    for (int64_t g = 0; g < G; ++g) {
+      const int64_t r0 = g * per, rows = (a->n - r0 < per) ? (a->n - r0) : per;
+      if (rows <= 0) break;
+      ThreadDev* td;
+      SC_TRY(thread_dev(devs[g], &td));
+      Shard sh;
+      sh.row0 = r0;
+      SC_TRY(make_data_block(devs[g], a->family, rows, a->k, a->x, a->ldx, a->x_row_major, a->y, a->y_is_double, r0,
+                             td->stream, &sh.d));
+      e->bytes += sh.d->bytes;
+      e->shards.push_back(sh);
+    }
+    e->last_use = ++g_cache_tick;
+    g_cache[key] = e;
+    *out = e;
+    return STAN_CUDA_OK;
+  }
   Key key;
   const bool with_y = !a->y_per_call;  // a per-call y is no part of the identity: keyed on x alone
   const int64_t kind_bits = int64_t(a->family) * 8 + (a->y_per_call ? 4 : 0) + a->x_row_major * 2 + a->y_is_double +
@@ -309,6 +355,7 @@ struct ShardRun {
   ThreadDev* td = nullptr;
   double *d_params = nullptr, *d_result = nullptr, *d_alpha = nullptr, *d_sigma = nullptr, *d_rowa = nullptr,
          *d_rows = nullptr;
+  double* d_dx = nullptr;     // var x: d * beta^T, column-major rows x k
   void* d_y = nullptr;        // per-call outcomes (y_per_call)
   double y_lgamma_sum = 0.0;
 };
@@ -337,7 +384,8 @@ int glm_eval(const stan_cuda_glm_args* a) {
   // Per-call outcomes: y goes to the device now (padded to whole tiles like the cached copy) into a buffer of
   // its own; integer outcomes also get their range and sum lgamma(y + 1) recomputed.
   int64_t call_lo = INT64_MAX, call_hi = INT64_MIN;
-  if (a->y_per_call) {
+  const bool y_call = a->y_per_call && !a->x_per_call;  // (a per-call x refills y along with it)
+  if (y_call) {
     const size_t ysz = a->y_is_double ? sizeof(double) : sizeof(int32_t);
     for (size_t s = 0; s < S; ++s) {
       stan_cuda_data* d = e->shards[s].d;
@@ -368,7 +416,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
       lo = std::min(lo, e->shards[s].d->y_min);
       hi = std::max(hi, e->shards[s].d->y_max);
     }
-    if (a->y_per_call) {
+    if (y_call) {
       lo = call_lo;
       hi = call_hi;
     }
@@ -386,9 +434,16 @@ int glm_eval(const stan_cuda_glm_args* a) {
   }
   const bool alpha_vec = !ordered && !categorical && a->alpha_len != 1;
   const bool sigma_vec = has_scale(a->family) && a->sigma_len != 1;
-  const bool want_rowa = ((a->flags & STAN_CUDA_NEED_DALPHA) && alpha_vec && a->dalpha) ||
-                         ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID);
+  bool want_rowa = ((a->flags & STAN_CUDA_NEED_DALPHA) && alpha_vec && a->dalpha) ||
+                   ((a->flags & STAN_CUDA_NEED_DY) && a->dy && a->family == STAN_CUDA_NORMAL_ID);
   const bool want_rows = (a->flags & STAN_CUDA_NEED_DSIGMA) && sigma_vec && a->dsigma;
+  // var x: d/dx = d * beta^T needs d per row on the device (the ROWIO instantiation), then one outer-product kernel
+  const bool want_dx = (a->flags & STAN_CUDA_NEED_DX) && a->dx && a->k > 0;
+  if (want_dx && (categorical || ordered))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: d/dx is not available for ordered_logistic / categorical_logit");
+  if (want_dx && a->lddx < a->n) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: lddx < n");
+  const bool want_rowa_user = want_rowa;
+  want_rowa = want_rowa || want_dx;
   const int world = comm_world_size();
   if (world > 1 && S > 1) return fail(STAN_CUDA_ERR_STATE, "multi-process communicator with several devices per process");
 
@@ -436,6 +491,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (sigma_vec) need += rows_al;
     if (want_rowa) need += rows_al;
     if (want_rows) need += rows_al;
+    if (want_dx) need += size_t(rows) * size_t(a->k);
     SC_TRY(td->reserve_dev(need));
     double* p = td->d_buf;
     run.d_params = p; p += (np + 1) & ~size_t(1);
@@ -444,6 +500,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     if (sigma_vec) { run.d_sigma = p; p += rows_al; }
     if (want_rowa) { run.d_rowa = p; p += rows_al; }
     if (want_rows) { run.d_rows = p; p += rows_al; }
+    if (want_dx) { run.d_dx = p; p += size_t(rows) * size_t(a->k); }
     double* hp = td->h_pinned;
     if (categorical) {  // weights class-major, every class padded to kpad; intercepts behind
       for (size_t c = 0; c < ncls; ++c) {
@@ -479,6 +536,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
       io.host_seq = ++td->host_seq;
     }
     SC_TRY(launch_glm(d, io, &td->ws, td->stream));
+    if (want_dx) SC_TRY(launch_dx_outer(run.d_rowa, run.d_params, rows, a->k, run.d_dx, td->stream));
   }
   // combine the additive result blocks of the row shards (unless the kernel already did)
   if (xchg) {
@@ -526,7 +584,10 @@ int glm_eval(const stan_cuda_glm_args* a) {
     SC_CUDA(cudaSetDevice(d->device));
     if (s == 0)
       SC_CUDA(cudaMemcpyAsync(td->h_pinned + np, runs[s].d_result, nr * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
-    if (want_rowa) {
+    if (want_dx)
+      SC_CUDA(cudaMemcpy2DAsync(a->dx + r0, size_t(a->lddx) * sizeof(double), runs[s].d_dx, size_t(rows) * sizeof(double),
+                                size_t(rows) * sizeof(double), size_t(a->k), cudaMemcpyDeviceToHost, td->stream));
+    if (want_rowa_user) {
       double* dst = (alpha_vec && (a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha) ? a->dalpha : a->dy;
       SC_CUDA(cudaMemcpyAsync(dst + r0, runs[s].d_rowa, size_t(rows) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
     }
@@ -558,7 +619,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     a->aux[0] = res[1];
     a->aux[1] = res[3];
     a->aux[2] = 0.0;
-    a->aux[3] = a->y_per_call ? runs[0].y_lgamma_sum : e->shards[0].d->lgamma_sum;
+    a->aux[3] = y_call ? runs[0].y_lgamma_sum : e->shards[0].d->lgamma_sum;
   }
   counters().evals.fetch_add(1, std::memory_order_relaxed);
   return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;

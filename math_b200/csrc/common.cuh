@@ -146,6 +146,8 @@ constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sig
 // Enqueue the fused kernel for one data block.  ws must belong to the block's device.
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+// var x: dx[j * rows + i] = d[i] * params[j]  (d/dx = d * beta^T; data.cu)
+int launch_dx_outer(const double* d_row, const double* d_params, int64_t rows, int64_t k, double* dx, cudaStream_t stream);
 int launch_glm_colblocks(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);

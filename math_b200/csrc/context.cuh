@@ -38,6 +38,8 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
                     int x_row_major, const void* y, int y_is_double, int64_t row0, cudaStream_t stream,
                     stan_cuda_data** out);
 void free_data_block(stan_cuda_data* d);
+int refill_data_block(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_major, const void* y, int64_t row0,
+                      cudaStream_t stream);
 
 // Peer exchange (comm.cu): all-reduce fused into the GLM kernel over NVLink peer memory --------
 // Every device owns one exchange block; the last CTA of the fused kernel pushes its result block

@@ -134,6 +134,40 @@ int int_vector_stats(const int* d_y, int64_t n, int want_lgamma, cudaStream_t st
   return STAN_CUDA_OK;
 }
 
+// var x (bernoulli_logit_glm_lpmf.hpp:125-128, poisson_log_glm_lpmf.hpp:119-122, normal_id_glm_lpdf.hpp:121-124):
+// d/dx = (beta d^T)^T, an n x k outer product -- a pure HBM write stream of n * k * 8 bytes (the n + k inputs stay in
+// L1/L2).  One thread writes two consecutive rows of one column (16-byte stores, coalesced along the rows).
+__global__ void __launch_bounds__(256) dx_outer_kernel(const double* __restrict__ d_row, const double* __restrict__ beta,
+                                                       int64_t rows, int64_t k, double* __restrict__ dx) {
+  const int64_t pairs = (rows + 1) / 2;
+  const int64_t total = pairs * k;
+  for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < total; idx += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t j = idx / pairs, i = (idx - j * pairs) * 2;
+    const double b = beta[j];
+    double* dst = dx + j * rows + i;
+    if (i + 1 < rows && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+      *reinterpret_cast<double2*>(dst) = make_double2(d_row[i] * b, d_row[i + 1] * b);
+    } else {
+      dst[0] = d_row[i] * b;
+      if (i + 1 < rows) dst[1] = d_row[i + 1] * b;
+    }
+  }
+}
+
+int launch_dx_outer(const double* d_row, const double* d_params, int64_t rows, int64_t k, double* dx, cudaStream_t stream) {
+  if (rows <= 0 || k <= 0) return STAN_CUDA_OK;
+  int dev = 0;
+  SC_CUDA(cudaGetDevice(&dev));
+  const int64_t total = (rows + 1) / 2 * k;
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = int64_t(sm_count(dev)) * 8;
+  if (blocks > cap) blocks = cap;
+  dx_outer_kernel<<<unsigned(blocks), 256, 0, stream>>>(d_row, d_params, rows, k, dx);
+  SC_CUDA(cudaGetLastError());
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
+  return STAN_CUDA_OK;
+}
+
 static const size_t kStageBytes = size_t(256) << 20;  // staging buffer for the fill
 
 // Upload rows [row0, row0 + d->n) of the host matrix into d (already sized; d->t chosen).
@@ -145,8 +179,14 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
   const size_t x_bytes = size_t(t.tiles) * t.tile_bytes();
   const size_t y_elem = d->y_is_double ? sizeof(double) : sizeof(int);
   const size_t y_bytes = size_t(t.tiles) * t.R * y_elem;
-  SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d->x), x_bytes));
-  SC_CUDA(cudaMalloc(&d->y, y_bytes));
+  // (a refill of an existing block -- per-call x, refill_data_block -- keeps its allocations: same shape, same sizes)
+  if (!d->x) SC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d->x), x_bytes));
+  if (!d->y) SC_CUDA(cudaMalloc(&d->y, y_bytes));
+  if (d->hist) {
+    SC_CUDA(cudaFree(d->hist));
+    d->hist = nullptr;
+    d->hist_len = 0;
+  }
   d->bytes = x_bytes + y_bytes;
   // zero fill covers the padding columns [k, kpad) (padding rows are written by the retile kernel)
   if (t.kpad != k || x_row_major) SC_CUDA(cudaMemsetAsync(d->x, 0, x_bytes, stream));
@@ -334,6 +374,27 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
   counters().bytes_uploaded.fetch_add(up);
   counters().last_fill_ms.store(std::chrono::duration<double, std::milli>(t1 - t0).count());
   *out = d;
+  return STAN_CUDA_OK;
+}
+
+// Per-call x (stan_cuda_glm_args.x_per_call): the same shape again with new contents, into the block's existing
+// device buffers (no cudaMalloc / cudaFree per evaluation).
+int refill_data_block(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_major, const void* y, int64_t row0,
+                      cudaStream_t stream) {
+  uint64_t up = 0;
+  if (!d->colblocks.empty()) {
+    for (size_t b = 0; b < d->colblocks.size(); ++b) {
+      const int64_t c0 = int64_t(b) * kColBlock;
+      SC_TRY(refill_data_block(d->colblocks[b], x_row_major ? x + c0 : x + c0 * ldx, ldx, x_row_major, y, row0, stream));
+    }
+    const stan_cuda_data* last = d->colblocks.back();
+    d->lgamma_sum = last->lgamma_sum;
+    d->y_min = last->y_min;
+    d->y_max = last->y_max;
+    return STAN_CUDA_OK;
+  }
+  SC_TRY(upload_glm_data(d, x, ldx, x_row_major, y, row0, stream, &up));
+  counters().bytes_uploaded.fetch_add(up);
   return STAN_CUDA_OK;
 }
 

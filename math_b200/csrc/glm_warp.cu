@@ -548,7 +548,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
     return v ? atoi(v) : 1;
   }();
   const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
-  const bool pdl = pdl_on != 0 && !rowio && d->family <= STAN_CUDA_NORMAL_ID && !io.shared_gpu && !ws->fixed;
+  const bool pdl = pdl_on != 0 && !rowio && d->family <= STAN_CUDA_NORMAL_ID && !io.shared_gpu;
   if (pdl && grid64 == int64_t(sms) * ctas_per_sm && grid64 > pdl_slack + 8) grid64 -= pdl_slack;
   const int grid = int(grid64);
   int group_size = 1;

@@ -124,9 +124,12 @@ def glm_flags(family, propto, alpha_var=True, beta_var=True, sigma_var=True, y_v
     return f
 
 
-def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, need_dy=False, y_per_call=False):
+def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, need_dy=False, y_per_call=False,
+             need_dx=False, x_per_call=None):
     """Raw C-ABI call (no argument checks beyond shapes).  Returns dict with rc, lp and partials.
-    y_per_call: y is not immutable data (a parameter vector): cache keyed on x alone, y uploaded every call."""
+    y_per_call: y is not immutable data (a parameter vector): cache keyed on x alone, y uploaded every call.
+    need_dx: x is a parameter matrix: "dx" (n, k) = d * beta^T comes back, and (unless x_per_call=False) x is
+    uploaded on every call instead of being looked up in the cache."""
     fam = _abi.FAMILIES[family] if isinstance(family, str) else family
     x, row_major, ldx = _prep_x(x)
     n, k = x.shape
@@ -149,6 +152,12 @@ def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, ne
     a.x, a.ldx, a.x_row_major = x.ctypes.data, ldx, row_major
     a.y, a.y_is_double = y.ctypes.data, int(fam == _abi.NORMAL_ID)
     a.y_per_call = int(bool(y_per_call))
+    dx = None
+    if need_dx:
+        dx = np.zeros((max(n, 1), max(k, 1)), order="F")
+        a.flags = flags = flags | _abi.NEED_DX
+        a.dx, a.lddx = dx.ctypes.data, max(n, 1)
+    a.x_per_call = int(need_dx if x_per_call is None else bool(x_per_call))
     a.alpha, a.alpha_len, a.beta = alpha.ctypes.data, alpha.size, beta.ctypes.data
     if sigma is not None:
         a.sigma, a.sigma_len = sigma.ctypes.data, sigma.size
@@ -162,6 +171,8 @@ def glm_eval(family, y, x, alpha, beta, sigma=None, flags=None, propto=False, ne
         out["dsigma"] = dsigma[:sigma.size].copy()
     if dy is not None:
         out["dy"] = dy[:n].copy()
+    if dx is not None:
+        out["dx"] = dx[:n, :k].copy()
     return out
 
 

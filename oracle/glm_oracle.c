@@ -320,6 +320,14 @@ int oracle_glm_eval(const stan_cuda_glm_args* a) {
     default: free(d); return STAN_CUDA_ERR_ARG;
   }
   if (rc >= 0 && (a->flags & STAN_CUDA_NEED_DBETA) && a->dbeta) xt_times(a, d, a->dbeta);
+  /* var x: (beta * d^T)^T, i.e. dx_ij = d_i * beta_j (bernoulli_logit_glm_lpmf.hpp:125-128,
+   * poisson_log_glm_lpmf.hpp:119-122, normal_id_glm_lpdf.hpp:121-124, neg_binomial_2_log_glm_lpmf.hpp:163-167,
+   * ordered_logistic_glm_lpmf.hpp:186-190) */
+  if (rc >= 0 && (a->flags & STAN_CUDA_NEED_DX) && a->dx) {
+    const int64_t ld = a->lddx > 0 ? a->lddx : a->n;
+    for (int64_t j = 0; j < a->k; ++j)
+      for (int64_t i = 0; i < a->n; ++i) a->dx[j * ld + i] = a->beta[j] * d[i];
+  }
   free(d);
   return rc;
 }

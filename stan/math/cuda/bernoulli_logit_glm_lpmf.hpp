@@ -22,7 +22,7 @@ namespace cuda {
  * reports a non-finite log-density (:106-110).
  */
 template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta>
-return_type_t<T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y, const T_x& x,
+return_type_t<typename x_operand<T_x>::scalar, T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y, const T_x& x,
                                                                     const T_alpha& alpha, const T_beta& beta) {
   static const char* function = "bernoulli_logit_glm_lpmf";
   const size_t N = x.rows();
@@ -38,7 +38,7 @@ return_type_t<T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y, con
   if (size_zero(y)) {
     return 0;
   }
-  if (!include_summand<propto, double, T_alpha, T_beta>::value) {
+  if (!include_summand<propto, typename x_operand<T_x>::scalar, T_alpha, T_beta>::value) {
     check_bounded(function, "Vector of dependent variables", y, 0, 1);  // nothing goes to the device
     return 0;
   }
@@ -46,8 +46,7 @@ return_type_t<T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y, con
   int_outcome<T_y> y_val(y, N);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_BERNOULLI_LOGIT, x, alpha, beta);
   // x is data on this path: its (empty) edge is declared on a double so that views of x work too
-  const double x_placeholder = 0;
-  arena_partials<double, T_alpha, T_beta> ops_partials(x_placeholder, alpha, beta);
+  arena_partials<typename x_operand<T_x>::type, T_alpha, T_beta> ops_partials(x_operand<T_x>::get(x), alpha, beta);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_per_call = y_val.per_call() ? 1 : 0;
@@ -60,6 +59,11 @@ return_type_t<T_alpha, T_beta> bernoulli_logit_glm_lpmf_device(const T_y& y, con
   if (!is_constant_all<T_alpha>::value) {
     a.flags |= STAN_CUDA_NEED_DALPHA;
     a.dalpha = ops_partials.partials(1);
+  }
+  if (!is_constant_all<typename x_operand<T_x>::scalar>::value) {  // var x: d * beta^T into the x edge (N x K, column-major)
+    a.flags |= STAN_CUDA_NEED_DX;
+    a.dx = ops_partials.partials(0);
+    a.lddx = N;
   }
   int rc = call.run(function);
   if (rc == STAN_CUDA_BAD_OUTCOME) {

@@ -6,6 +6,7 @@
 #include <stan/math/cuda/err.hpp>
 #include <stan/math/cuda/marshal.hpp>
 #include <string>
+#include <utility>
 #include <system_error>
 #include <vector>
 
@@ -22,12 +23,13 @@ template <typename T_x, typename T_alpha, typename T_beta>
 class glm_call {
  public:
   glm_call(int family, const T_x& x, const T_alpha& alpha, const T_beta& beta)
-      : alpha_val_(alpha), beta_val_(beta), logp_(0) {
+      : x_val_(x), alpha_val_(alpha), beta_val_(beta), logp_(0) {
     a_ = stan_cuda_glm_args();
     a_.family = family;
     a_.n = x.rows();
     a_.k = x.cols();
-    matrix_layout(x, &a_.x, &a_.ldx, &a_.x_row_major);
+    matrix_layout(x_val_.matrix(), &a_.x, &a_.ldx, &a_.x_row_major);
+    a_.x_per_call = x_val_.per_call() ? 1 : 0;
     a_.alpha = alpha_val_.data();
     a_.alpha_len = alpha_val_.size();
     if (beta_val_.size() == static_cast<size_t>(a_.k)) {
@@ -97,9 +99,9 @@ class glm_call {
 
   /** Host recomputation of X * beta + alpha, used only on the error path so that the reference's
    * own check_finite call sees the same object it would have seen. */
-  Eigen::Matrix<double, Eigen::Dynamic, 1> host_linear_predictor(const T_x& x) const {
+  Eigen::Matrix<double, Eigen::Dynamic, 1> host_linear_predictor(const T_x& /*x*/) const {
     Eigen::Map<const Eigen::Matrix<double, Eigen::Dynamic, 1>> b(a_.beta, a_.k);
-    Eigen::Matrix<double, Eigen::Dynamic, 1> theta = x * b;
+    Eigen::Matrix<double, Eigen::Dynamic, 1> theta = x_val_.matrix() * b;
     if (a_.alpha_len == 1) {
       theta.array() += a_.alpha[0];
     } else {
@@ -109,6 +111,7 @@ class glm_call {
   }
 
  private:
+  design_values<T_x> x_val_;
   values<T_alpha> alpha_val_;
   values<T_beta> beta_val_;
   std::vector<double> beta_bcast_;

@@ -70,6 +70,32 @@ typedef Eigen::Map<const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>> 
 template <>
 struct is_data_matrix<data_matrix_view> : std::true_type {};
 
+/** x as a parameter: a column-major Eigen matrix of var.  Its values are gathered into a
+ * temporary on every call and travel to the device with it (stan_cuda_glm_args.x_per_call); the N x K partials
+ * d * beta^T come back into the x edge of the tape node. */
+template <typename T>
+struct is_var_matrix : std::false_type {};
+template <int O, int MR, int MC>
+struct is_var_matrix<Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic, O, MR, MC>>
+    : std::integral_constant<bool, (O & Eigen::RowMajor) == 0> {};
+template <typename T>
+struct is_design_matrix : std::integral_constant<bool, is_data_matrix<T>::value || is_var_matrix<T>::value> {};
+
+/** What the x argument contributes to the tape node: nothing (declared on a double, so that views of data work
+ * too) for data, the matrix itself for a var matrix. */
+template <typename T_x>
+struct x_operand {
+  typedef double type;
+  typedef double scalar;
+  static double get(const T_x& /*x*/) { return 0.0; }
+};
+template <int O, int MR, int MC>
+struct x_operand<Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic, O, MR, MC>> {
+  typedef Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic, O, MR, MC> type;
+  typedef var scalar;
+  static const type& get(const type& x) { return x; }
+};
+
 /** scalar, std::vector or Eigen vector whose scalar type satisfies Pred */
 template <typename T, template <typename> class Pred>
 struct is_scalar_or_vector_of : Pred<T> {};
@@ -97,12 +123,12 @@ struct is_real_outcome : is_scalar_or_vector_of<T, is_double_or_var> {};
 
 template <typename T_y, typename T_x, typename T_alpha, typename T_beta>
 struct int_glm_eligible
-    : std::integral_constant<bool, is_int_outcome<T_y>::value && is_data_matrix<T_x>::value
+    : std::integral_constant<bool, is_int_outcome<T_y>::value && is_design_matrix<T_x>::value
                                        && is_param_arg<T_alpha>::value && is_param_arg<T_beta>::value> {};
 
 template <typename T_y, typename T_x, typename T_alpha, typename T_beta, typename T_scale>
 struct normal_glm_eligible
-    : std::integral_constant<bool, is_real_outcome<T_y>::value && is_data_matrix<T_x>::value
+    : std::integral_constant<bool, is_real_outcome<T_y>::value && is_design_matrix<T_x>::value
                                        && is_param_arg<T_alpha>::value && is_param_arg<T_beta>::value
                                        && is_param_arg<T_scale>::value> {};
 
@@ -254,6 +280,37 @@ template <int R, int C>
 inline double* partials_data(internal::ops_partials_edge<double, Eigen::Matrix<var, R, C>>& edge) {
   return edge.partials_.data();
 }
+
+/** The design matrix as doubles: data is borrowed, a var matrix is gathered (in parallel) into a temporary. */
+template <typename T_x>
+class design_values {
+ public:
+  explicit design_values(const T_x& x) : x_(x) {}
+  const T_x& matrix() const { return x_; }
+  bool per_call() const { return false; }
+
+ private:
+  const T_x& x_;
+};
+template <int O, int MR, int MC>
+class design_values<Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic, O, MR, MC>> {
+ public:
+  typedef Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic, O, MR, MC> T_x;
+  explicit design_values(const T_x& x) : vals_(x.rows(), x.cols()) {
+    const var* src = x.data();  // column-major (is_var_matrix): same order as the values and as the x edge
+    double* dst = vals_.data();
+    for_each_chunk(static_cast<size_t>(x.size()), [&](size_t begin, size_t end) {
+      for (size_t i = begin; i != end; ++i) {
+        dst[i] = src[i].vi_->val_;
+      }
+    });
+  }
+  const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>& matrix() const { return vals_; }
+  bool per_call() const { return true; }
+
+ private:
+  Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic> vals_;
+};
 
 /** Matrix layout as the C ABI wants it. */
 template <int R, int C, int O, int MR, int MC>

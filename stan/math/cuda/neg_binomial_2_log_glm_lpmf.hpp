@@ -17,7 +17,7 @@ namespace cuda {
 
 template <typename T_y, typename T_x, typename T_alpha, typename T_beta, typename T_precision>
 struct neg_binomial_glm_eligible
-    : std::integral_constant<bool, is_int_outcome<T_y>::value && is_data_matrix<T_x>::value
+    : std::integral_constant<bool, is_int_outcome<T_y>::value && is_design_matrix<T_x>::value
                                        && is_param_arg<T_alpha>::value && is_param_arg<T_beta>::value
                                        && is_param_arg<T_precision>::value> {};
 
@@ -30,7 +30,7 @@ struct neg_binomial_glm_eligible
  * include_summand exactly as :130-153.
  */
 template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta, typename T_precision>
-return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(const T_y& y, const T_x& x,
+return_type_t<typename x_operand<T_x>::scalar, T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(const T_y& y, const T_x& x,
                                                                                const T_alpha& alpha,
                                                                                const T_beta& beta,
                                                                                const T_precision& phi) {
@@ -46,7 +46,7 @@ return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(c
   if (is_vector<T_alpha>::value) {
     check_consistent_sizes(function, "Vector of intercepts", alpha, "Vector of dependent variables", y);
   }
-  if (size_zero(y, phi) || !include_summand<propto, double, T_alpha, T_beta, T_precision>::value) {
+  if (size_zero(y, phi) || !include_summand<propto, typename x_operand<T_x>::scalar, T_alpha, T_beta, T_precision>::value) {
     check_nonnegative(function, "Failures variables", y);  // nothing goes to the device
     check_finite(function, "Weight vector", beta);
     check_finite(function, "Intercept", alpha);
@@ -57,8 +57,8 @@ return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(c
   int_outcome<T_y> y_val(y, N);
   values<T_precision> phi_val(phi);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_NEG_BINOMIAL_2_LOG, x, alpha, beta);
-  const double x_placeholder = 0;
-  arena_partials<double, T_alpha, T_beta, T_precision> ops_partials(x_placeholder, alpha, beta, phi);
+  arena_partials<typename x_operand<T_x>::type, T_alpha, T_beta, T_precision> ops_partials(x_operand<T_x>::get(x), alpha, beta,
+                                                                                           phi);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_per_call = y_val.per_call() ? 1 : 0;
@@ -72,7 +72,7 @@ return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(c
   if (include_summand<propto, T_precision>::value) {
     a.flags |= STAN_CUDA_LP_SCALE;
   }
-  if (include_summand<propto, double, T_alpha, T_beta>::value) {
+  if (include_summand<propto, typename x_operand<T_x>::scalar, T_alpha, T_beta>::value) {
     a.flags |= STAN_CUDA_LP_LINEAR;
   }
   if (!is_constant_all<T_beta>::value) {
@@ -86,6 +86,11 @@ return_type_t<T_alpha, T_beta, T_precision> neg_binomial_2_log_glm_lpmf_device(c
   if (!is_constant_all<T_precision>::value) {
     a.flags |= STAN_CUDA_NEED_DSIGMA;
     a.dsigma = ops_partials.partials(3);
+  }
+  if (!is_constant_all<typename x_operand<T_x>::scalar>::value) {  // var x: theta_derivative * beta^T into the x edge (:163-168)
+    a.flags |= STAN_CUDA_NEED_DX;
+    a.dx = ops_partials.partials(0);
+    a.lddx = N;
   }
   // eager O(K) parameter checks, after the outcome check in the reference's order
   int rc = STAN_CUDA_OK;

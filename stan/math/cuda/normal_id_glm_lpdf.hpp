@@ -20,7 +20,7 @@ namespace cuda {
  * alpha, beta, sigma go straight into edges 1, 3, 4, 5; lazy checks as :150-156.
  */
 template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta, typename T_scale>
-return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y& y, const T_x& x,
+return_type_t<T_y, typename x_operand<T_x>::scalar, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y& y, const T_x& x,
                                                                             const T_alpha& alpha,
                                                                             const T_beta& beta,
                                                                             const T_scale& sigma) {
@@ -40,7 +40,7 @@ return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y
   if (size_zero(y, sigma)) {
     return 0;
   }
-  if (!include_summand<propto, T_y, double, T_alpha, T_beta, T_scale>::value) {
+  if (!include_summand<propto, T_y, typename x_operand<T_x>::scalar, T_alpha, T_beta, T_scale>::value) {
     return 0;
   }
 
@@ -48,8 +48,8 @@ return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y
   values<T_scale> sigma_val(sigma);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_NORMAL_ID, x, alpha, beta);
   // x is data on this path: its (empty) edge is declared on a double so that views of x work too
-  const double x_placeholder = 0;
-  arena_partials<T_y, double, T_alpha, T_beta, T_scale> ops_partials(y, x_placeholder, alpha, beta, sigma);
+  arena_partials<T_y, typename x_operand<T_x>::type, T_alpha, T_beta, T_scale> ops_partials(y, x_operand<T_x>::get(x), alpha,
+                                                                                          beta, sigma);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_per_call = y_val.per_call() ? 1 : 0;
@@ -81,6 +81,11 @@ return_type_t<T_y, T_alpha, T_beta, T_scale> normal_id_glm_lpdf_device(const T_y
   if (!is_constant_all<T_scale>::value) {
     a.flags |= STAN_CUDA_NEED_DSIGMA;
     a.dsigma = ops_partials.partials(4);
+  }
+  if (!is_constant_all<typename x_operand<T_x>::scalar>::value) {  // var x: mu_derivative * beta^T into the x edge (:121-124)
+    a.flags |= STAN_CUDA_NEED_DX;
+    a.dx = ops_partials.partials(1);
+    a.lddx = N;
   }
   if (call.run(function) == STAN_CUDA_NONFINITE) {
     const double y_scaled_sq_sum = call.witness();

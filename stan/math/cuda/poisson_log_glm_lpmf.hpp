@@ -21,7 +21,7 @@ namespace cuda {
  * is true, so the propto variant returns 0 with a non-zero gradient.
  */
 template <bool propto, typename T_y, typename T_x, typename T_alpha, typename T_beta>
-return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T_x& x, const T_alpha& alpha,
+return_type_t<typename x_operand<T_x>::scalar, T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T_x& x, const T_alpha& alpha,
                                                                 const T_beta& beta) {
   static const char* function = "poisson_log_glm_lpmf";
   using T_partials_return = partials_return_t<T_y, double, T_alpha, T_beta>;
@@ -38,7 +38,7 @@ return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T
   if (size_zero(y)) {
     return 0;
   }
-  if (!include_summand<propto, double, T_alpha, T_beta>::value) {
+  if (!include_summand<propto, typename x_operand<T_x>::scalar, T_alpha, T_beta>::value) {
     check_nonnegative(function, "Vector of dependent variables", y);  // nothing goes to the device
     return 0;
   }
@@ -46,8 +46,7 @@ return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T
   int_outcome<T_y> y_val(y, N);
   glm_call<T_x, T_alpha, T_beta> call(STAN_CUDA_POISSON_LOG, x, alpha, beta);
   // x is data on this path: its (empty) edge is declared on a double so that views of x work too
-  const double x_placeholder = 0;
-  arena_partials<double, T_alpha, T_beta> ops_partials(x_placeholder, alpha, beta);
+  arena_partials<typename x_operand<T_x>::type, T_alpha, T_beta> ops_partials(x_operand<T_x>::get(x), alpha, beta);
   stan_cuda_glm_args& a = call.args();
   a.y = y_val.data();
   a.y_per_call = y_val.per_call() ? 1 : 0;
@@ -66,6 +65,11 @@ return_type_t<T_alpha, T_beta> poisson_log_glm_lpmf_device(const T_y& y, const T
   if (!is_constant_all<T_alpha>::value) {
     a.flags |= STAN_CUDA_NEED_DALPHA;
     a.dalpha = ops_partials.partials(1);
+  }
+  if (!is_constant_all<typename x_operand<T_x>::scalar>::value) {  // var x: d * beta^T into the x edge (N x K, column-major)
+    a.flags |= STAN_CUDA_NEED_DX;
+    a.dx = ops_partials.partials(0);
+    a.lddx = N;
   }
   int rc = call.run(function);
   if (rc == STAN_CUDA_BAD_OUTCOME) {

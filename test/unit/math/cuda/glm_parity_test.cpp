@@ -194,6 +194,44 @@ TEST(CudaGlmVariants, wide_matrix_vector_alpha_vector_sigma_var_y) {
   stan::math::recover_memory();
 }
 
+TEST(CudaGlmVariants, var_design_matrix) {
+  // x as a parameter -- d/dx = d * beta^T (bernoulli_logit_glm_lpmf.hpp:125-128,
+  // poisson_log_glm_lpmf.hpp:119-122, normal_id_glm_lpdf.hpp:121-124), the reference's 3 x 2 fixture shape and larger
+  const int shapes[4][2] = {{3, 2}, {153, 71}, {2000, 128}, {300, 600}};
+  for (int q = 0; q < 4; ++q) {
+    Problem p = make_problem(shapes[q][0], shapes[q][1], 40 + q);
+    Matrix<var, Dynamic, Dynamic> xv(p.x.rows(), p.x.cols());
+    for (int64_t i = 0; i < p.x.size(); ++i) xv.data()[i] = p.x.data()[i];
+    auto adj_x = [&]() {
+      VectorXd g(xv.size());
+      for (int64_t i = 0; i < xv.size(); ++i) g[i] = xv.data()[i].adj();
+      return g;
+    };
+    vector_v beta = to_v(p.beta), alpha_v = to_v(p.alpha_vec);
+    var alpha = p.alpha, sigma = p.sigma, phi = 2.5;
+    using namespace stan::math;  // NOLINT
+    STAN_CUDA_PARITY("bernoulli var x", bernoulli_logit_glm_lpmf(p.y_bern, xv, alpha, beta),
+                     bernoulli_logit_glm_lpmf_reference_cpu(p.y_bern, xv, alpha, beta), adj(beta),
+                     VectorXd::Constant(1, alpha.adj()), adj_x());
+    STAN_CUDA_PARITY("poisson var x, vector alpha", poisson_log_glm_lpmf(p.y_pois, xv, alpha_v, beta),
+                     poisson_log_glm_lpmf_reference_cpu(p.y_pois, xv, alpha_v, beta), adj(beta), adj(alpha_v), adj_x());
+    STAN_CUDA_PARITY("poisson var x only", poisson_log_glm_lpmf(p.y_pois, xv, p.alpha, p.beta),
+                     poisson_log_glm_lpmf_reference_cpu(p.y_pois, xv, p.alpha, p.beta), adj_x());
+    STAN_CUDA_PARITY("normal_id var x", normal_id_glm_lpdf(p.y_norm, xv, alpha, beta, sigma),
+                     normal_id_glm_lpdf_reference_cpu(p.y_norm, xv, alpha, beta, sigma), adj(beta),
+                     VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, sigma.adj()), adj_x());
+    STAN_CUDA_PARITY("neg_binomial_2_log var x", neg_binomial_2_log_glm_lpmf(p.y_pois, xv, alpha, beta, phi),
+                     neg_binomial_2_log_glm_lpmf_reference_cpu(p.y_pois, xv, alpha, beta, phi), adj(beta),
+                     VectorXd::Constant(1, alpha.adj()), VectorXd::Constant(1, phi.adj()), adj_x());
+    // the values of x change between calls: nothing may be served from a cache
+    for (int64_t i = 0; i < xv.size(); ++i) xv.data()[i] = 0.5 * p.x.data()[i];
+    STAN_CUDA_PARITY("bernoulli var x, new values at the same shape", bernoulli_logit_glm_lpmf(p.y_bern, xv, alpha, beta),
+                     bernoulli_logit_glm_lpmf_reference_cpu(p.y_bern, xv, alpha, beta), adj(beta),
+                     VectorXd::Constant(1, alpha.adj()), adj_x());
+    stan::math::recover_memory();
+  }
+}
+
 TEST(CudaGlmVariants, ordered_logistic) {
   using stan::math::ordered_logistic_glm_lpmf;
   using stan::math::ordered_logistic_glm_lpmf_reference_cpu;

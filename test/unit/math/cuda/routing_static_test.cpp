@@ -28,19 +28,21 @@ static_assert(cu::int_glm_eligible<ints, matrix_d, double, vector_d>::value, "al
 static_assert(cu::int_glm_eligible<int, matrix_d, var, row_vector_v>::value, "scalar y, row vector beta");
 static_assert(cu::int_glm_eligible<vector_i, matrix_d, vector_v, std::vector<var>>::value, "Eigen int y, vector alpha");
 static_assert(cu::int_glm_eligible<ints, cu::data_matrix_view, var, vector_v>::value, "zero-copy view");
-static_assert(!cu::int_glm_eligible<ints, matrix_v, var, vector_v>::value, "var x stays on the reference body");
+static_assert(cu::int_glm_eligible<ints, matrix_v, var, vector_v>::value, "var x (column-major): device path, N x K partials");
+static_assert(!cu::int_glm_eligible<ints, Matrix<var, Dynamic, Dynamic, Eigen::RowMajor>, var, vector_v>::value, "row-major var x stays on the reference body");
+static_assert(!cu::int_glm_eligible<ints, Matrix<fvar<double>, Dynamic, Dynamic>, double, vector_d>::value, "fvar x stays on the reference body");
 static_assert(!cu::int_glm_eligible<ints, matrix_d, fvar<double>, vector_fd>::value, "fvar stays on the reference body");
 static_assert(!cu::int_glm_eligible<vector_d, matrix_d, var, vector_v>::value, "real outcomes are not int outcomes");
 // normal_id_glm (normal_id_glm_lpdf.hpp:49-53, interface test :441-478)
 static_assert(cu::normal_glm_eligible<vector_d, matrix_d, var, vector_v, var>::value, "C4 signature");
 static_assert(cu::normal_glm_eligible<vector_v, matrix_d, vector_v, vector_v, vector_v>::value, "var y, vector alpha/sigma");
 static_assert(cu::normal_glm_eligible<double, matrix_d, double, vector_d, double>::value, "scalar y");
-static_assert(!cu::normal_glm_eligible<vector_d, matrix_v, var, vector_v, var>::value, "var x");
+static_assert(cu::normal_glm_eligible<vector_d, matrix_v, var, vector_v, var>::value, "var x: device path");
 static_assert(!cu::normal_glm_eligible<vector_fd, matrix_d, double, vector_d, double>::value, "fvar y");
 // neg_binomial_2_log_glm
 static_assert(cu::neg_binomial_glm_eligible<ints, matrix_d, var, vector_v, var>::value, "scalar phi");
 static_assert(cu::neg_binomial_glm_eligible<ints, matrix_d, vector_v, vector_v, vector_v>::value, "vector alpha / phi");
-static_assert(!cu::neg_binomial_glm_eligible<ints, matrix_v, var, vector_v, var>::value, "var x");
+static_assert(cu::neg_binomial_glm_eligible<ints, matrix_v, var, vector_v, var>::value, "var x: device path");
 // ordered_logistic_glm / categorical_logit_glm (std::vector<int> y, dynamic data matrix)
 static_assert(cu::ordered_logistic_glm_eligible<ints, double, Dynamic, var, var>::value, "var beta, var cuts");
 static_assert(cu::ordered_logistic_glm_eligible<ints, double, Dynamic, double, double>::value, "all double");
