@@ -325,7 +325,7 @@ static int check_glm_args(const stan_cuda_glm_args* a) {
   } else if (a->family == STAN_CUDA_ORDERED_LOGISTIC) {
     if (a->cuts_len < 0 || (a->cuts_len > 0 && !a->cuts)) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null cuts");
     if (a->cuts_len > kMaxCuts)
-      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: ordered_logistic supports at most 256 cut-points on the device");
+      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: ordered_logistic supports at most 1024 cut-points on the device");
   } else if (!a->alpha || (a->alpha_len != 1 && a->alpha_len != a->n)) {
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: alpha_len must be 1 or n");
   }
@@ -599,6 +599,14 @@ int glm_eval(const stan_cuda_glm_args* a) {
     SC_CUDA(cudaStreamSynchronize(runs[s].td->stream));
   }
   const double* res = runs[0].td->h_pinned + np;
+  if (xchg) {
+    // the in-kernel exchange gives up after 30 s without a peer's block and marks every result with this NaN payload
+    uint64_t bits;
+    memcpy(&bits, &res[0], 8);
+    if (bits == 0x7ff8dead00000000ull)
+      return fail(STAN_CUDA_ERR_NCCL, "fused all-reduce: a peer device did not publish its result block within 30 s "
+                                      "(a rank died, or the ranks did not launch the same sequence of sharded evaluations)");
+  }
   if (a->lp) *a->lp = res[0];
   if (categorical) {
     if ((a->flags & STAN_CUDA_NEED_DALPHA) && a->dalpha) memcpy(a->dalpha, res + 4, ncls * sizeof(double));

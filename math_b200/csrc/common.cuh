@@ -139,7 +139,7 @@ constexpr int kFamilyLinearBlock = 6;
 constexpr int kColBlock = 512;               // columns per block: the widest tile of the warp kernel (C = 32, kc = 16)
 constexpr int kMaxClasses = 16;              // categorical_logit: classes on the device path
 constexpr int kMaxClassWeights = 4096;       // categorical_logit: classes * k_pad (weights live in shared memory)
-constexpr int kMaxCuts = 256;                // ordered_logistic: per-warp bins live in shared memory
+constexpr int kMaxCuts = 1024;               // ordered_logistic: per-warp bins and the class table live in shared memory
 constexpr int kOrdPrivateDoubles = 2048;     // ordered_logistic: ncuts * R up to this -> one private bin row per row slot
 constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sigma)
 

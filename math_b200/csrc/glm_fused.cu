@@ -364,7 +364,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->pdl = 0;
   p->ncls = 0;
   p->cat_groups = 1;
-  if (p->ncuts < 0 || p->ncuts > kMaxCuts) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
+  if (p->ncuts < 0 || p->ncuts > kMaxCuts) return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 1024 cut-points on the device");
   p->x = d->x;
   p->y = io.d_y ? io.d_y : d->y;
   p->n = d->n;

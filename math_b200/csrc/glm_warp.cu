@@ -372,7 +372,8 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
     }
     my_scratch[c] = sum;
   }
-  double* fin = reinterpret_cast<double*>(stage0);  // [cols]; every stage has been consumed by now
+  double* fin = red;  // [cols]: the warps' partials were summed into my_scratch above (finish_reduction starts with a barrier);
+                      // `red` holds 8 x cols doubles whatever the tile shape, the stages may be smaller than cols
   finish_reduction<FAMILY, NT>(p, tid, cols, part, fin, &s_flag, [] { consumer_sync(); });
 }
 
@@ -509,7 +510,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   const size_t budget = (size_t(228) * 1024) / ctas_per_sm - 1024 - 64;
   const int ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
   if (ncuts < 0 || ncuts > kMaxCuts)
-    return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 1024 cut-points on the device");
   const size_t cols = size_t(t.kpad) + 4 + ncuts;
   int stages = tuning().stages;
   size_t stage_bytes = 0;
@@ -736,7 +737,7 @@ int launch_glm_colblocks(const stan_cuda_data* d, const LaunchIO& io, Workspace*
   const stan_cuda_data* last = d->colblocks[size_t(B) - 1];
   const int ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
   if (ncuts < 0 || ncuts > kMaxCuts)
-    return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 256 cut-points on the device");
+    return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 1024 cut-points on the device");
   const int kpad_last = last->t.kpad;
   const size_t np_stride = size_t(kColBlock) + 2 + ncuts, nr_stride = size_t(kColBlock) + 4 + ncuts;
   const size_t rows_al = (size_t(d->n) + 1) & ~size_t(1);

@@ -109,10 +109,18 @@ def test_ordered_logistic_error_contract(glm):
     # single class / no instances: 0 after the checks (:88-89)
     assert f([1, 1, 1, 1, 1], x, beta, [])[0] == 0.0
     assert f([], np.zeros((0, 2)), beta, cuts)[0] == 0.0
-    # more cut-points than the device path holds: loud error, no fallback
+    # 300 cut-points (round 1 stopped at 256): parity with the oracle
+    from oracle import loader as L
+    so = synth_ordered(4001, 24, 301, seed=21)
+    lp, g = f(so["y"], so["x"], so["beta"], so["cuts"])
+    o = L.oracle_ordered_logistic_glm(so["x"], so["y"], so["beta"], so["cuts"])
+    assert_close(lp, o["lp"], "ordered 301 classes lp")
+    assert_close(g["beta"], o["dbeta"], "ordered 301 classes dbeta")
+    assert_close(g["cuts"], o["dcuts"], "ordered 301 classes dcuts")
+    # more cut-points than the class table in shared memory holds: loud error, no fallback
     with pytest.raises(Exception) as e:
-        f([1] * 5, x, beta, np.arange(300.0))
-    assert "256" in str(e.value)
+        f([1] * 5, x, beta, np.arange(1100.0))
+    assert "1024" in str(e.value)
 
 
 CAT_FLAGS = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA
