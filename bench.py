@@ -360,6 +360,9 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    if args.kernel == "cta" and os.environ.get("STAN_CUDA_WITH_CTA_KERNEL") != "1":
+        raise SystemExit("bench.py: --kernel cta needs a library built with STAN_CUDA_WITH_CTA_KERNEL=1 (the superseded "
+                         "CTA-synchronous variant is not part of the product build)")
     family, n, k, desc = WORKLOADS[args.workload]
     if args.workload in ("c1", "c5"):
         run_cxx_workload(args, args.workload, desc)

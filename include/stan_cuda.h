@@ -229,9 +229,10 @@ STAN_CUDA_API void stan_cuda_set_shard_min_elems(int64_t elems);
  * pipeline stages and resident CTAs per SM.  0 = automatic, negative = leave unchanged.
  * Environment: STAN_CUDA_THREADS / STAN_CUDA_STAGES / STAN_CUDA_CTAS_PER_SM. */
 STAN_CUDA_API void stan_cuda_set_tuning(int threads, int stages, int ctas_per_sm);
-/* Kernel variant for data created afterwards: 1 (default) = warp-synchronous kernel with a TMA
- * producer warp (csrc/glm_warp.cu), 0 = CTA-synchronous kernel (csrc/glm_fused.cu).  Both compute
- * the same thing from differently tiled copies of X.  Environment: STAN_CUDA_KERNEL=warp|cta. */
+/* Kernel variant for data created afterwards: 1 (default) = warp-synchronous kernel (csrc/glm_warp.cu), 0 = the
+ * CTA-synchronous kernel it superseded (csrc/glm_fused.cu), present only in a library built with
+ * STAN_CUDA_WITH_CTA_KERNEL=1 (A/B measurements); in the product build the call is accepted and ignored.
+ * Environment: STAN_CUDA_KERNEL=warp|cta. */
 STAN_CUDA_API void stan_cuda_set_kernel(int variant);
 /* categorical_logit kernel for data created afterwards: 1 (default) = FP64 tensor-core kernel (mma.m8n8k4,
  * SASS DMMA) on a tile layout stored in the instruction's fragment order (csrc/glm_categorical_mma.cu;

@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "math_b200", "csrc")
 LIB_DIR = os.path.join(ROOT, "math_b200", "lib")
 LIB = os.path.join(LIB_DIR, "libstanmath_cuda.so")
-SOURCES = ["glm_fused.cu", "glm_warp.cu", "glm_categorical.cu", "glm_categorical_mma.cu", "normal_lpdf.cu", "density.cu", "data.cu", "context.cu", "comm.cu", "api.cu"]
+SOURCES = ["glm_fused.cu", "glm_warp.cu", "glm_categorical.cu", "glm_categorical_mma.cu", "glm_categorical_wide.cu", "normal_lpdf.cu", "density.cu", "data.cu", "context.cu", "comm.cu", "api.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-diag-suppress", "177"]
 
@@ -30,6 +30,11 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def cta_kernel_flags():
+    """The superseded CTA-synchronous kernel (csrc/glm_fused.cu) is compiled in only on request."""
+    return ("-DSTAN_CUDA_WITH_CTA_KERNEL",) if os.environ.get("STAN_CUDA_WITH_CTA_KERNEL") == "1" else ()
+
+
 def build(force=False, verbose=False, variant="", extra_flags=()):
     """Compile every .cu into an object (parallel) and link the shared library.  `variant` names a
     debugging build (e.g. "timers" with -DSTAN_CUDA_PHASE_TIMERS, used by tools/phase_timers.py);
@@ -46,7 +51,7 @@ def build(force=False, verbose=False, variant="", extra_flags=()):
         o = os.path.join(obj_dir, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _stale(o, [s] + headers):
-            cmd = [nvcc()] + NVCC_FLAGS + list(extra_flags) + ["-c", s, "-o", o]
+            cmd = [nvcc()] + NVCC_FLAGS + list(cta_kernel_flags()) + list(extra_flags) + ["-c", s, "-o", o]
             if verbose:
                 print(" ".join(cmd))
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))

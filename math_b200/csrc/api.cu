@@ -207,6 +207,7 @@ static std::vector<int> pick_devices(int64_t n, int64_t k) {
 }
 
 static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* out) {
+  set_categorical_classes_hint(a->family == STAN_CUDA_CATEGORICAL_LOGIT ? a->n_classes : 0);  // picks the data layout
   if (a->x_per_call) {
     // var x: nothing to recognise -- the calling thread keeps one set of device buffers per (shape, family) and
     // refills it on every call (upload + re-tiling; no cudaMalloc after the first call of that shape)
@@ -255,8 +256,9 @@ static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* ou
   }
   Key key;
   const bool with_y = !a->y_per_call;  // a per-call y is no part of the identity: keyed on x alone
+  const bool cat_wide = a->family == STAN_CUDA_CATEGORICAL_LOGIT && categorical_is_wide(a->k, a->n_classes);
   const int64_t kind_bits = int64_t(a->family) * 8 + (a->y_per_call ? 4 : 0) + a->x_row_major * 2 + a->y_is_double +
-                            64 * tuning().layout + 256 * tuning().cat_mma;
+                            64 * tuning().layout + 256 * tuning().cat_mma + 512 * (cat_wide ? 1 : 0);
   if (tl_scope.active) {
     // (call_id, job) is the identity of a job's immutable data (mpi_parallel_call.hpp:40-89); a functor may make
     // SEVERAL GLM calls per job (one design matrix, two outcome vectors ...): the ordinal of the call inside the
@@ -320,8 +322,6 @@ static int check_glm_args(const stan_cuda_glm_args* a) {
   if (a->family == STAN_CUDA_CATEGORICAL_LOGIT) {
     if (a->n_classes < 1 || !a->alpha || a->alpha_len != a->n_classes)
       return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit needs n_classes >= 1 and alpha_len == n_classes");
-    if (a->n_classes > kMaxClasses)
-      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit supports at most 16 classes on the device");
   } else if (a->family == STAN_CUDA_ORDERED_LOGISTIC) {
     if (a->cuts_len < 0 || (a->cuts_len > 0 && !a->cuts)) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null cuts");
     if (a->cuts_len > kMaxCuts)
@@ -465,8 +465,6 @@ int glm_eval(const stan_cuda_glm_args* a) {
   }
 
   const int kpad = e->shards[0].d->t.kpad;
-  if (categorical && ncls * size_t(kpad) > size_t(kMaxClassWeights))
-    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit supports classes * k_pad <= 4096 on the device");
   const size_t np = categorical ? ncls * (size_t(kpad) + 1) : size_t(kpad) + 2 + ncuts;
   const size_t nr = categorical ? 4 + ncls * (size_t(kpad) + 1) : size_t(kpad) + 4 + ncuts;
   if (xchg && nr > size_t(kXchgCols)) xchg = nullptr;  // result block wider than an exchange slot: NCCL behind the kernel

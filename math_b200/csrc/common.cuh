@@ -49,6 +49,7 @@ constexpr int kMaxKc = 16;
 constexpr int kLayoutCta = 0;
 constexpr int kLayoutWarp = 1;
 constexpr int kLayoutMma = 2;
+constexpr int kLayoutPlain = 3;  // glm_categorical_wide.cu: plain column-major (one "tile" of R = padded row count)
 
 struct Tiling {
   int layout;   // kLayoutCta | kLayoutWarp
@@ -151,6 +152,14 @@ int launch_dx_outer(const double* d_row, const double* d_params, int64_t rows, i
 int launch_glm_colblocks(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+int launch_glm_categorical_wide(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+// categorical_logit shapes outside the two fused kernels (weights in shared memory: <= 16 classes, classes * k_pad <= 4096,
+// k <= 512) run on the general three-pass path over plain column-major data (glm_categorical_wide.cu)
+inline bool categorical_is_wide(int64_t k, int64_t ncls) {
+  return ncls > 16 || k > 512 || ncls * ((k + 15) / 16 * 16) > 4096;
+}
+// number of classes of the categorical_logit call for which the next data block of this thread is created (0: unknown)
+void set_categorical_classes_hint(int64_t ncls);
 // width of the result block (and of every partial) of one launch
 inline size_t result_cols(const stan_cuda_data* d, const LaunchIO& io) {
   if (d->family == STAN_CUDA_CATEGORICAL_LOGIT) return size_t(4) + size_t(io.ncls) * (d->t.kpad + 1);

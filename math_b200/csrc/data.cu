@@ -19,7 +19,7 @@ struct TileMap {
   int layout, R, C, kc, kpad;
 };
 __device__ __forceinline__ int64_t tile_elem_offset(const TileMap& m, int r, int col) {
-  if (m.layout == kLayoutCta) return int64_t(col) * m.R + r;
+  if (m.layout == kLayoutCta || m.layout == kLayoutPlain) return int64_t(col) * m.R + r;
   if (m.layout == kLayoutMma) return (int64_t(r >> 3) * (m.kpad >> 2) + (col >> 2)) * 32 + (r & 7) * 4 + (col & 3);
   const int rpw = 32 / m.C;
   const int w = r / rpw, rl = r - w * rpw;
@@ -302,6 +302,9 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
   return STAN_CUDA_OK;
 }
 
+static thread_local int64_t tl_categorical_classes = 0;
+void set_categorical_classes_hint(int64_t ncls) { tl_categorical_classes = ncls; }
+
 static thread_local bool tl_block_of_wider_matrix = false;  // set while the column blocks of a k > 512 matrix are built
 
 int make_data_block(int device, int family, int64_t n_rows, int64_t k, const double* x, int64_t ldx,
@@ -356,9 +359,16 @@ int make_data_block(int device, int family, int64_t n_rows, int64_t k, const dou
   // kernels: FP64 tensor-core (fragment layout, k <= 256) or vector (warp layout)
   int force = (family >= STAN_CUDA_NEG_BINOMIAL_2_LOG || tl_block_of_wider_matrix) ? kLayoutWarp : -1;
   if (family == STAN_CUDA_CATEGORICAL_LOGIT && tuning().cat_mma && k <= 256) force = kLayoutMma;
+  if (family == STAN_CUDA_CATEGORICAL_LOGIT && tl_categorical_classes > 0 && categorical_is_wide(k, tl_categorical_classes))
+    force = kLayoutPlain;
+  if (force == kLayoutPlain && n_rows >= (int64_t(1) << 31) - 2) {
+    delete d;
+    return fail(STAN_CUDA_ERR_ARG, "data block: the general categorical_logit path holds fewer than 2^31 rows per device");
+  }
   if (!choose_tiling(n_rows, k, 0, &d->t, force)) {
     delete d;
-    return fail(STAN_CUDA_ERR_ARG, "data block: k > 512 is outside the fused kernel's range");
+    return fail(STAN_CUDA_ERR_ARG, "data block: categorical_logit with k > 512 needs the number of classes (stan_cuda_glm_eval); "
+                                   "the device-level stan_cuda_data_create serves k <= 512");
   }
   auto t0 = std::chrono::steady_clock::now();
   uint64_t up = 0;
@@ -428,6 +438,7 @@ int stan_cuda_data_create(int family, int64_t n, int64_t k, const double* x, int
   if (!ok) dev = context().devices[0];
   ThreadDev* td;
   SC_TRY(thread_dev(dev, &td));
+  set_categorical_classes_hint(0);  // the number of classes is unknown here: the fused kernels' layouts
   return make_data_block(dev, family, n, k, x, ldx, x_row_major, y, y_is_double, 0, td->stream, out);
 }
 

@@ -28,6 +28,10 @@
 
 namespace stancuda {
 
+// The CTA-synchronous kernel was superseded by glm_warp.cu in round 1 and is kept for A/B measurements only: it is
+// compiled into the library when the build defines STAN_CUDA_WITH_CTA_KERNEL (math_b200/build.py, environment
+// STAN_CUDA_WITH_CTA_KERNEL=1); the product library carries the warp kernel alone.
+#ifdef STAN_CUDA_WITH_CTA_KERNEL
 // Sum `v` over the `width` consecutive lanes that share a column group (width = min(R, 32)).
 __device__ __forceinline__ double group_reduce(double v, int width) {
 #pragma unroll
@@ -212,6 +216,8 @@ glm_fused_kernel(const GlmKernelParams p) {
   finish_reduction<FAMILY, THREADS>(p, tid, cols, part, fin, &s_is_last, [] { __syncthreads(); });
 }
 
+#endif  // STAN_CUDA_WITH_CTA_KERNEL
+
 }  // namespace stancuda
 
 // =============================================================================================
@@ -234,7 +240,12 @@ static Tuning& tuning_mut() {
     const char* sv = getenv("STAN_CUDA_SCHEDULE");
     u.blocked = (sv && (sv[0] == 'b' || sv[0] == 'B')) ? 1 : 0;
     const char* kv = getenv("STAN_CUDA_KERNEL");
+#ifdef STAN_CUDA_WITH_CTA_KERNEL
     u.layout = (kv && (kv[0] == 'c' || kv[0] == 'C')) ? kLayoutCta : kLayoutWarp;
+#else
+    (void)kv;
+    u.layout = kLayoutWarp;
+#endif
     const char* cv = getenv("STAN_CUDA_CATEGORICAL");
     u.cat_mma = (cv && (cv[0] == 'w' || cv[0] == 'W' || cv[0] == 'v' || cv[0] == 'V')) ? 0 : 1;
     return u;
@@ -258,6 +269,16 @@ int sm_count(int device) {
 bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t, int force_layout) {
   if (k < 1) k = 1;
   const int layout = force_layout >= 0 ? force_layout : tuning().layout;
+  if (layout == kLayoutPlain) {
+    t->layout = kLayoutPlain;
+    t->threads = 256;
+    t->C = 1;
+    t->kc = int(k);
+    t->kpad = int(k);
+    t->R = int((n + 1) & ~int64_t(1));
+    t->tiles = 1;
+    return true;
+  }
   if (layout == kLayoutMma) {
     // fragments of 8 rows x 4 columns (glm_categorical_mma.cu); tiles of at most 32 KiB up to 64 columns
     if (k > 256) return false;
@@ -304,6 +325,7 @@ bool choose_tiling(int64_t n, int64_t k, int threads_override, Tiling* t, int fo
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+#ifdef STAN_CUDA_WITH_CTA_KERNEL
 template <int FAMILY, int THREADS, bool ROWIO>
 static int launch_inst(const GlmKernelParams& p, int grid, size_t smem, cudaStream_t stream) {
   auto kern = glm_fused_kernel<FAMILY, THREADS, ROWIO>;
@@ -344,6 +366,8 @@ static size_t smem_bytes(const Tiling& t, int stages, size_t* stage_bytes_out) {
                        + size_t(stages) * sizeof(uint64_t);
   return size_t(stages) * stage + fixed;
 }
+
+#endif  // STAN_CUDA_WITH_CTA_KERNEL
 
 #ifdef STAN_CUDA_PHASE_TIMERS
 static unsigned long long* g_phase_timers = nullptr;  // debugging build only (tools/phase_timers.py)
@@ -415,11 +439,16 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   if (!d->colblocks.empty()) return launch_glm_colblocks(d, io, ws, stream);  // k > 512
   const Tiling& t = d->t;
+  if (d->family == STAN_CUDA_CATEGORICAL_LOGIT && t.layout == kLayoutPlain) return launch_glm_categorical_wide(d, io, ws, stream);
   if (d->family == STAN_CUDA_CATEGORICAL_LOGIT)
     return t.layout == kLayoutMma ? launch_glm_categorical_mma(d, io, ws, stream) : launch_glm_categorical(d, io, ws, stream);
   if (t.layout == kLayoutWarp) return launch_glm_warp(d, io, ws, stream);
   if (d->family >= STAN_CUDA_NEG_BINOMIAL_2_LOG)
     return fail(STAN_CUDA_ERR_ARG, "launch_glm: neg_binomial_2_log and ordered_logistic run on the warp kernel only");
+#ifndef STAN_CUDA_WITH_CTA_KERNEL
+  return fail(STAN_CUDA_ERR_STATE, "launch_glm: this library was built without the CTA-synchronous kernel variant "
+                                   "(STAN_CUDA_WITH_CTA_KERNEL)");
+#else
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
   const int sms = sm_count(d->device);
   int ctas_per_sm = tuning().ctas_per_sm;
@@ -460,6 +489,7 @@ int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaS
       return launch_family<STAN_CUDA_NORMAL_ID>(rowio, t.threads, p, grid, smem, stream);
   }
   return fail(STAN_CUDA_ERR_ARG, "launch_glm: unknown family");
+#endif  // STAN_CUDA_WITH_CTA_KERNEL
 }
 
 }  // namespace stancuda
@@ -471,7 +501,12 @@ extern "C" STAN_CUDA_API void stan_cuda_debug_set_timers(unsigned long long* dev
 #endif
 
 extern "C" void stan_cuda_set_kernel(int variant) {
+#ifdef STAN_CUDA_WITH_CTA_KERNEL
   stancuda::tuning_mut().layout = variant == 0 ? stancuda::kLayoutCta : stancuda::kLayoutWarp;
+#else
+  (void)variant;  // built without the superseded variant: the warp kernel is the only one
+  stancuda::tuning_mut().layout = stancuda::kLayoutWarp;
+#endif
 }
 
 extern "C" void stan_cuda_set_categorical_kernel(int variant) { stancuda::tuning_mut().cat_mma = variant == 1 ? 1 : 0; }

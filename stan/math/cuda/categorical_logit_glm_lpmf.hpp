@@ -31,8 +31,9 @@ struct categorical_logit_glm_eligible
  * stan/math/prim/mat/prob/categorical_logit_glm_lpmf.hpp:38-190).  Size checks :56-62 unchanged;
  * check_bounded(y, 1, N_classes) :63-64 is answered by the device from the range of y computed at
  * cache fill; the lazy finiteness checks :109-113 run on the host only when the device reports a
- * non-finite log-density.  Device limits (16 classes, classes * padded attributes <= 4096) are
- * reported as std::system_error.
+ * non-finite log-density.  Any shape is served: up to 16 classes with classes * padded attributes <= 4096 and at most
+ * 512 attributes by the fused single-pass kernels, everything else by the general three-pass path
+ * (csrc/glm_categorical_wide.cu).
  */
 template <bool propto, typename T_alpha_scalar, typename T_beta_scalar>
 return_type_t<T_alpha_scalar, T_beta_scalar> categorical_logit_glm_lpmf_device(

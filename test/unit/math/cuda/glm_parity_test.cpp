@@ -296,6 +296,37 @@ TEST(CudaGlmVariants, categorical_logit) {
   EXPECT_THROW(categorical_logit_glm_lpmf(y_low, p.x, alpha, beta), std::domain_error);
 }
 
+TEST(CudaGlmVariants, categorical_logit_beyond_the_fused_kernels) {
+  // more than 16 classes, classes * attributes > 4096, more than 512 attributes: the general path
+  // (csrc/glm_categorical_wide.cu); round 1 raised std::system_error for these shapes
+  using stan::math::categorical_logit_glm_lpmf;
+  using stan::math::categorical_logit_glm_lpmf_reference_cpu;
+  typedef Eigen::Matrix<var, Dynamic, Dynamic> matrix_v;
+  const int shapes[3][3] = {{2001, 29, 17}, {1501, 300, 16}, {701, 600, 4}};
+  for (int q = 0; q < 3; ++q) {
+    const int n = shapes[q][0], k = shapes[q][1], C = shapes[q][2];
+    Problem p = make_problem(n, k, 50 + q);
+    std::mt19937_64 rng(78 + q);
+    std::normal_distribution<double> nd(0.0, 0.6 / std::sqrt(double(k)));
+    MatrixXd beta_d(k, C);
+    VectorXd alpha_d(C);
+    for (int i = 0; i < beta_d.size(); ++i) beta_d(i) = nd(rng);
+    for (int c = 0; c < C; ++c) alpha_d[c] = nd(rng);
+    std::vector<int> y(n);
+    for (int i = 0; i < n; ++i) y[i] = 1 + (p.y_pois[i] + i) % C;
+    matrix_v beta = beta_d.cast<var>();
+    vector_v alpha = to_v(alpha_d);
+    auto adj_m = [](const matrix_v& m) {
+      VectorXd g(m.size());
+      for (int i = 0; i < m.size(); ++i) g[i] = m(i).adj();
+      return g;
+    };
+    STAN_CUDA_PARITY("categorical_logit general path", categorical_logit_glm_lpmf(y, p.x, alpha, beta),
+                     categorical_logit_glm_lpmf_reference_cpu(y, p.x, alpha, beta), adj_m(beta), adj(alpha));
+    stan::math::recover_memory();
+  }
+}
+
 TEST(CudaGlmVariants, zero_copy_data_view) {
   Problem p = make_problem(4001, 37, 9);
   vector_v beta = to_v(p.beta);

@@ -13,8 +13,9 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module", params=["warp", "cta"])
 def glm(request):
-    """The whole module runs once per kernel variant (csrc/glm_warp.cu, csrc/glm_fused.cu); the categorical_logit
-    cases run on the DMMA kernel in the first pass (the default) and on the vector kernel in the second."""
+    """The whole module runs twice: the categorical_logit cases run on the DMMA kernel in the first pass (the default)
+    and on the vector kernel in the second; the second pass also selects the superseded CTA-synchronous GLM kernel
+    (csrc/glm_fused.cu) where the library was built with it (STAN_CUDA_WITH_CTA_KERNEL=1; ignored by the product build)."""
     from math_b200 import glm as g
     from math_b200._lib import lib
     g.init(1)
@@ -187,9 +188,18 @@ def test_categorical_logit_error_contract(glm):
         with pytest.raises(glm.DomainError):
             f(y, x, av, beta)
     assert f([1] * 5, x, [0.3], beta[:, :1])[0] == 0.0      # single class (:66-68)
-    with pytest.raises(Exception) as e:                      # beyond the device limit: loud, no fallback
-        f([1] * 5, x, np.zeros(17), np.zeros((2, 17)))
-    assert "16" in str(e.value)
+    # shapes beyond the fused kernels (round 1 raised here): the general three-pass path, parity with the oracle
+    from oracle import loader as L
+    for n, k, ncls in ((5, 2, 17), (4001, 40, 17), (3001, 24, 64), (2001, 600, 5), (1501, 300, 16)):
+        sc = synth_categorical(n, k, ncls, seed=ncls + k)
+        lp, g = f(sc["y"], sc["x"], sc["alpha"], sc["beta"])
+        o = L.oracle_categorical_logit_glm(sc["x"], sc["y"], sc["alpha"], sc["beta"])
+        what = "categorical %dx%d, %d classes" % (n, k, ncls)
+        assert_close(lp, o["lp"], what + " lp")
+        assert_close(g["alpha"], o["dalpha"], what + " dalpha")
+        assert_close(np.asarray(g["beta"]).ravel(order="F"), np.asarray(o["dbeta"]).ravel(order="F"), what + " dbeta")
+        lp2, g2 = f(sc["y"], sc["x"], sc["alpha"], sc["beta"])
+        assert lp2 == lp and np.array_equal(g2["beta"], g["beta"])   # bit-reproducible
 
 
 def test_golden_normal_cases(glm, golden):
