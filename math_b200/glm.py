@@ -545,6 +545,43 @@ def poisson_log_lpmf(n, alpha, propto=False, alpha_var=True):
                     DomainError("%s: Random variable must be >= 0!" % f), "Log rate parameter")
 
 
+class GlmCall:
+    """One GLM evaluated many times at changing parameters through the host-level C-ABI call stan_cuda_glm_eval with
+    HOST buffers: the argument block and the input / output arrays are built once, `eval(alpha, beta, sigma)` copies
+    the parameters in and makes the call -- what a compiled caller (the C++ wrappers) does per evaluation, without
+    the per-call array allocations of `glm_eval`.  Families bernoulli_logit / poisson_log / normal_id /
+    neg_binomial_2_log with scalar intercept and scale."""
+
+    def __init__(self, family, y, x, flags=None):
+        fam = _abi.FAMILIES[family] if isinstance(family, str) else family
+        x, row_major, ldx = _prep_x(x)
+        n, k = x.shape
+        y = _f64(y) if fam == _abi.NORMAL_ID else np.ascontiguousarray(np.atleast_1d(np.asarray(y, dtype=np.int32)))
+        self.fam, self.n, self.k, self.x, self.y = fam, n, k, x, y
+        self.alpha, self.beta, self.sigma = np.zeros(1), np.zeros(max(k, 1)), np.ones(1)
+        self.lp, self.dbeta, self.dalpha, self.dsigma, self.aux = np.zeros(1), np.zeros(max(k, 1)), np.zeros(1), np.zeros(1), np.zeros(4)
+        a = self.args = _abi.GlmArgs()
+        a.family, a.flags, a.n, a.k = fam, (glm_flags(fam, False) if flags is None else flags), n, k
+        a.x, a.ldx, a.x_row_major = x.ctypes.data, ldx, row_major
+        a.y, a.y_is_double = y.ctypes.data, int(fam == _abi.NORMAL_ID)
+        a.alpha, a.alpha_len, a.beta = self.alpha.ctypes.data, 1, self.beta.ctypes.data
+        if fam in _abi.HAS_SCALE:
+            a.sigma, a.sigma_len = self.sigma.ctypes.data, 1
+        a.lp, a.dbeta, a.dalpha, a.dsigma = (self.lp.ctypes.data, self.dbeta.ctypes.data, self.dalpha.ctypes.data,
+                                             self.dsigma.ctypes.data)
+        a.aux = self.aux.ctypes.data
+        self._ref = C.byref(a)
+        self._fn = lib().stan_cuda_glm_eval
+
+    def eval(self, alpha, beta, sigma=None):
+        """Returns the C-ABI return code; results are in self.lp[0], self.dbeta[:k], self.dalpha[0], self.dsigma[0]."""
+        self.alpha[0] = alpha
+        self.beta[:self.k] = beta
+        if sigma is not None:
+            self.sigma[0] = sigma
+        return check(self._fn(self._ref))
+
+
 class GlmData:
     """Device-resident (x, y) of one GLM: the explicit form of the cache fill, for callers that
     own streams and device buffers themselves (bench.py via torch)."""

@@ -527,3 +527,20 @@ def test_shard_scope_keys_by_call_id_and_job(glm, L):
     st1 = glm.stats()
     assert st1["cache_misses"] - st0["cache_misses"] == 1 and st1["cache_hits"] - st0["cache_hits"] == 2
     glm.cache_clear()
+
+
+def test_prepared_call_matches_glm_eval(glm, L):
+    """math_b200.glm.GlmCall (argument block built once; what bench.py's end-to-end loop uses) against glm_eval and the oracle."""
+    for family in ("poisson_log", "normal_id"):
+        s = synth_glm(family, 30_001, 48, seed=31)
+        call = glm.GlmCall(family, s["y"], s["x"])
+        sg = None if s["sigma"] is None else float(s["sigma"][0])
+        for scale in (1.0, 1.05):
+            assert call.eval(s["alpha"][0], s["beta"] * scale, sg) == 0
+            ref = L.oracle_glm(family, s["x"], s["y"], s["alpha"], s["beta"] * scale, s["sigma"])
+            assert_close(call.lp[0], ref["lp"], family + " prepared call lp")
+            assert_close(call.dbeta[:48], ref["dbeta"], family + " prepared call dbeta")
+            assert_close(call.dalpha[0], ref["dalpha"][0], family + " prepared call dalpha")
+            same = glm.glm_eval(family, call.y, call.x, s["alpha"], s["beta"] * scale, s["sigma"])
+            assert same["lp"] == call.lp[0] and np.array_equal(same["dbeta"], call.dbeta[:48])
+    glm.cache_clear()
