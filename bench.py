@@ -561,7 +561,7 @@ def main():
                            else "ncclAllReduce behind the kernel") if world > 1 else None,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(args.workload) if world == 1 and not (args.n or args.k) else None,
-                         "traffic_source": "static: ncu --set full capture of this launch (profiles/traffic.json), "
+                         "traffic_source": "static: ncu --set full capture of this launch (profiles/traffic.json, profiles/r02_c3_glm_warp_raw.csv), "
                                            "not measured in this run",
                          "peak_source": peak_src,
                          "frac_of_nominal_8000": achieved / 8000.0,

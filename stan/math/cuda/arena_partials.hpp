@@ -18,45 +18,52 @@ namespace cuda {
 template <typename T>
 struct operand_edge {
   static size_t size(const T& /*v*/) { return 0; }
-  static void dump(const T& /*v*/, vari** /*dst*/) {}
+  static bool dump(const T& /*v*/, vari** /*dst*/) { return false; }
 };
 template <>
 struct operand_edge<var> {
   static size_t size(const var& /*v*/) { return 1; }
-  static void dump(const var& v, vari** dst) { dst[0] = v.vi_; }
+  static bool dump(const var& v, vari** dst) {
+    dst[0] = v.vi_;
+    return false;
+  }
 };
-inline void dump_var_array(const var* v, size_t n, vari** dst) {
+
+/** smallest edge for which the adjoint scatter of chain() is spread over the TBB workers */
+constexpr size_t bulk_chain_min = size_t(1) << 17;
+
+/**
+ * Copies the vari pointers of an edge into the tape node's operand array.  For a large edge the same pass also
+ * answers whether the addresses are strictly ascending -- which proves that no vari occurs twice, so the adjoint
+ * updates of different elements never touch the same memory (it is what a vector of parameters built element after
+ * element on the autodiff arena looks like).  Returns that answer (false for small edges: they keep the serial loop).
+ */
+inline bool dump_var_array(const var* v, size_t n, vari** dst) {
+#ifdef STAN_THREADS
+  if (n >= bulk_chain_min) {
+    std::atomic<bool> ascending(true);
+    for_each_chunk(n, [&](size_t begin, size_t end) {
+      bool mine = true;
+      uintptr_t prev = begin > 0 ? reinterpret_cast<uintptr_t>(v[begin - 1].vi_) : 0;
+      for (size_t i = begin; i != end; ++i) {
+        vari* p = v[i].vi_;
+        dst[i] = p;
+        mine = mine && prev < reinterpret_cast<uintptr_t>(p);
+        prev = reinterpret_cast<uintptr_t>(p);
+      }
+      if (!mine) {
+        ascending.store(false, std::memory_order_relaxed);
+      }
+    });
+    return ascending.load();
+  }
+#endif
   for_each_chunk(n, [&](size_t begin, size_t end) {
     for (size_t i = begin; i != end; ++i) {
       dst[i] = v[i].vi_;
     }
   });
-}
-
-/** smallest edge for which the adjoint scatter of chain() is spread over the TBB workers */
-constexpr size_t bulk_chain_min = size_t(1) << 17;
-
-/** true when the operand addresses of an edge are strictly ascending -- which proves that no vari occurs twice,
- * so the adjoint updates of different elements never touch the same memory.  It is what a vector of parameters
- * built element after element on the autodiff arena looks like; anything else keeps the serial loop. */
-inline bool strictly_ascending(vari* const* v, size_t n) {
-#ifdef STAN_THREADS
-  std::atomic<bool> ok(true);
-  for_each_chunk(n, [&](size_t begin, size_t end) {
-    bool mine = true;
-    for (size_t i = begin > 0 ? begin : 1; i < end; ++i) {
-      mine = mine && (reinterpret_cast<uintptr_t>(v[i - 1]) < reinterpret_cast<uintptr_t>(v[i]));
-    }
-    if (!mine) {
-      ok.store(false, std::memory_order_relaxed);
-    }
-  });
-  return ok.load();
-#else
-  (void)v;
-  (void)n;
   return false;
-#endif
 }
 
 /**
@@ -105,13 +112,13 @@ class bulk_gradients_vari : public precomputed_gradients_vari {
 template <>
 struct operand_edge<std::vector<var>> {
   static size_t size(const std::vector<var>& v) { return v.size(); }
-  static void dump(const std::vector<var>& v, vari** dst) { dump_var_array(v.data(), v.size(), dst); }
+  static bool dump(const std::vector<var>& v, vari** dst) { return dump_var_array(v.data(), v.size(), dst); }
 };
 template <int R, int C, int O, int MR, int MC>
 struct operand_edge<Eigen::Matrix<var, R, C, O, MR, MC>> {
   typedef Eigen::Matrix<var, R, C, O, MR, MC> T;
   static size_t size(const T& v) { return v.size(); }
-  static void dump(const T& v, vari** dst) { dump_var_array(v.data(), v.size(), dst); }
+  static bool dump(const T& v, vari** dst) { return dump_var_array(v.data(), v.size(), dst); }
 };
 
 /**
@@ -143,14 +150,17 @@ class arena_partials {
     }
     varis_ = nullptr;
     partials_ = nullptr;
+    for (int e = 0; e < 5; ++e) {
+      distinct_[e] = false;
+    }
     if (off_[5] > 0) {
       varis_ = ChainableStack::instance_->memalloc_.alloc_array<vari*>(off_[5]);
       partials_ = ChainableStack::instance_->memalloc_.alloc_array<double>(off_[5]);
-      operand_edge<T1>::dump(o1, varis_ + off_[0]);
-      operand_edge<T2>::dump(o2, varis_ + off_[1]);
-      operand_edge<T3>::dump(o3, varis_ + off_[2]);
-      operand_edge<T4>::dump(o4, varis_ + off_[3]);
-      operand_edge<T5>::dump(o5, varis_ + off_[4]);
+      distinct_[0] = operand_edge<T1>::dump(o1, varis_ + off_[0]);
+      distinct_[1] = operand_edge<T2>::dump(o2, varis_ + off_[1]);
+      distinct_[2] = operand_edge<T3>::dump(o3, varis_ + off_[2]);
+      distinct_[3] = operand_edge<T4>::dump(o4, varis_ + off_[3]);
+      distinct_[4] = operand_edge<T5>::dump(o5, varis_ + off_[4]);
       for (int e = 0; e < 5; ++e) {  // small edges start from zero like operands_and_partials' (cheap insurance);
         if (n_[e] <= 4096) {         // an N-element edge is written entirely by the device
           zero(e);
@@ -175,19 +185,18 @@ class arena_partials {
  private:
   double build(double value, std::true_type /*all arithmetic*/) const { return value; }
   var build(double value, std::false_type) const {
-    bool par[5];
     bool any = false;
     for (int e = 0; e < 5; ++e) {
-      par[e] = n_[e] >= bulk_chain_min && strictly_ascending(varis_ + off_[e], n_[e]);
-      any = any || par[e];
+      any = any || distinct_[e];
     }
-    if (any) {  // N-element edges: the adjoint scatter of chain() runs over the TBB workers
-      return var(new bulk_gradients_vari(value, off_[5], varis_, partials_, off_, par));
+    if (any) {  // N-element edges of provably distinct operands: the adjoint scatter of chain() runs over the TBB workers
+      return var(new bulk_gradients_vari(value, off_[5], varis_, partials_, off_, distinct_));
     }
     return var(new precomputed_gradients_vari(value, off_[5], varis_, partials_));
   }
   size_t n_[5];
   size_t off_[6];
+  bool distinct_[5];  // edge e is large and its operand addresses ascend strictly (see dump_var_array)
   vari** varis_;
   double* partials_;
 };
