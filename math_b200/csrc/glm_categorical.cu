@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(kCatThreads, 2) glm_categorical_kernel(const G
   uint64_t* full = reinterpret_cast<uint64_t*>(part + NT);                           // [stages]
   __shared__ int s_flag;
 
+  if (p.pdl) pdl_launch_dependents();  // the next evaluation may start under this one's tail (see glm_warp.cu)
   const int grid = gridDim.x;
   const int64_t tile0 = blockIdx.x;
   const int64_t tstride = grid;
@@ -208,6 +209,7 @@ __global__ void __launch_bounds__(kCatThreads, 2) glm_categorical_kernel(const G
     }
   }
   __syncthreads();
+  if (p.pdl) pdl_wait();  // first write to memory the previous evaluation also uses
   double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
   if (tid == 0) {
     double sum = 0.0;
@@ -250,7 +252,7 @@ static int launch_cat_inst(const GlmKernelParams& p, int grid, size_t smem, cuda
     SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     configured[dev].store(smem, std::memory_order_relaxed);
   }
-  kern<<<grid, kCatThreads, smem, stream>>>(p);
+  SC_CUDA(launch_maybe_pdl(kern, dim3(unsigned(grid)), dim3(kCatThreads), smem, stream, p.pdl != 0, p));
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
@@ -279,6 +281,8 @@ int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspac
 
   int64_t grid64 = int64_t(sms) * 2;
   if (grid64 > t.tiles) grid64 = t.tiles;
+  const bool pdl = pdl_enabled() && !io.shared_gpu;
+  if (pdl && grid64 == int64_t(sms) * 2 && grid64 > pdl_slack() + 8) grid64 -= pdl_slack();
   const int grid = int(grid64);
   int group_size = 1;
   while (group_size * group_size < grid) ++group_size;
@@ -291,6 +295,7 @@ int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspac
   p.stages = stages;
   p.group_size = group_size;
   p.stage_bytes = uint32_t(stage_bytes);
+  p.pdl = pdl ? 1 : 0;
   p.ncls = ncls;
   int G = 1;  // class groups: power of two <= 8 with G * CPG >= ncls, CPG <= 2
   while (G < kCatWarps && G * 2 < ncls) G <<= 1;

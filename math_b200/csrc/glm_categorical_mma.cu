@@ -78,6 +78,7 @@ __global__ void __launch_bounds__(kMmaThreads, TPR == 4 ? 3 : 2) glm_categorical
   uint64_t* full = reinterpret_cast<uint64_t*>(part + NT * 4);                          // [stages]
   __shared__ int s_flag;
 
+  if (p.pdl) pdl_launch_dependents();  // the next evaluation may start under this one's tail (see glm_warp.cu)
   const int grid = gridDim.x;
   const int64_t tile0 = blockIdx.x;
   const int64_t tstride = grid;
@@ -299,6 +300,7 @@ __global__ void __launch_bounds__(kMmaThreads, TPR == 4 ? 3 : 2) glm_categorical
 #pragma unroll
   for (int i = 0; i < 4; ++i) part[tid * 4 + i] = i < CPT ? da[i < CPT ? i : 0] : 0.0;
   __syncthreads();
+  if (p.pdl) pdl_wait();  // first write to memory the previous evaluation also uses
   double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
   for (int idx = tid; idx < ncls * kpad; idx += NT) {
     const int c = idx / kpad, k = idx - c * kpad;
@@ -350,7 +352,7 @@ static int launch_mma_inst(const GlmKernelParams& p, int grid, size_t smem, cuda
     SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     configured[dev].store(smem, std::memory_order_relaxed);
   }
-  kern<<<grid, kMmaThreads, smem, stream>>>(p);
+  SC_CUDA(launch_maybe_pdl(kern, dim3(unsigned(grid)), dim3(kMmaThreads), smem, stream, p.pdl != 0, p));
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
@@ -398,6 +400,8 @@ int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Work
 
   int64_t grid64 = int64_t(sms) * ctas_per_sm;
   if (grid64 > t.tiles) grid64 = t.tiles;
+  const bool pdl = pdl_enabled() && !io.shared_gpu;
+  if (pdl && grid64 == int64_t(sms) * ctas_per_sm && grid64 > pdl_slack() + 8) grid64 -= pdl_slack();
   const int grid = int(grid64);
   int group_size = 1;
   while (group_size * group_size < grid) ++group_size;
@@ -410,6 +414,7 @@ int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Work
   p.stages = stages;
   p.group_size = group_size;
   p.stage_bytes = uint32_t(stage_bytes);
+  p.pdl = pdl ? 1 : 0;
   p.ncls = ncls;
   if (t.R == 64) {  // k_pad <= 64: one m-tile per warp, four threads per row in the softmax phase
     const int cpt = (ncls + 3) / 4;

@@ -53,6 +53,28 @@ struct GlmKernelParams {
 #endif
 };
 
+// Programmatic dependent launch (see glm_warp.cu): STAN_CUDA_PDL=0 switches it off, STAN_CUDA_PDL_SLACK = CTA slots a
+// full-width grid leaves free for the previous evaluation's last CTA (default 1).
+bool pdl_enabled();
+int pdl_slack();
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <typename Kern, typename Params>
+inline cudaError_t launch_maybe_pdl(Kern kern, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, bool pdl,
+                                    const Params& p) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, p);
+}
+
 __device__ __forceinline__ double kernel_param(const GlmKernelParams& p, int i) {
   return p.inline_n > 0 ? p.inline_params[i] : p.params[i];
 }

@@ -89,7 +89,7 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
   // slots) is touched before the griddepcontrol.wait further down, and everything it reads before that point (X, y,
   // the parameter block) is never written by a GLM kernel -- so the tile loop of evaluation n + 1 overlaps the tail of
   // evaluation n.  Kernels with per-row outputs (ROWIO, the column-block chain) are launched without the attribute.
-  if (p.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (p.pdl) pdl_launch_dependents();
   PHASE_STAMP(0);
   if (tid == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -359,7 +359,7 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
   }
   consumer_sync();
   // first write to memory shared with the previous evaluation: wait until that grid has completed and flushed
-  if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (p.pdl) pdl_wait();
   double* my_scratch = p.scratch + size_t(blockIdx.x) * cols;
   for (int c = tid; c < cols; c += NT) {
     double sum = 0.0;
@@ -394,6 +394,21 @@ __global__ void __launch_bounds__(kWarpThreads, 2) glm_warp_batch_kernel(const G
 // =============================================================================================
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+bool pdl_enabled() {
+  static const int on = [] {
+    const char* v = getenv("STAN_CUDA_PDL");
+    return v ? atoi(v) : 1;
+  }();
+  return on != 0;
+}
+int pdl_slack() {
+  static const int slack = [] {
+    const char* v = getenv("STAN_CUDA_PDL_SLACK");
+    return v ? atoi(v) : 1;
+  }();
+  return slack;
+}
+
 static bool pair_mode(const Tiling& t) {
   static const int on = [] {
     const char* v = getenv("STAN_CUDA_PAIR");  // STAN_CUDA_PAIR=0: one tile per iteration (A/B)
@@ -422,21 +437,7 @@ static int launch_warp_inst2(const GlmKernelParams& p, int grid, size_t smem, cu
     SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     configured[dev].store(smem, std::memory_order_relaxed);
   }
-  if (p.pdl) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(unsigned(grid), 1, 1);
-    cfg.blockDim = dim3(kWarpThreads, 1, 1);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    SC_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
-  } else {
-    kern<<<grid, kWarpThreads, smem, stream>>>(p);
-  }
+  SC_CUDA(launch_maybe_pdl(kern, dim3(unsigned(grid)), dim3(kWarpThreads), smem, stream, p.pdl != 0, p));
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
@@ -459,6 +460,9 @@ static int launch_warp_inst(const GlmKernelParams& p, int grid, size_t smem, cud
 __global__ void __launch_bounds__(256) nb_hist_sums_kernel(const unsigned int* __restrict__ hist, int len,
                                                            const double* d_params, int phi_index, double phi_inline,
                                                            int use_inline, double* __restrict__ out) {
+  // In the dependent-launch chain GLM(n) -> this kernel -> GLM(n + 1): let GLM(n + 1) start right away; the two sums go
+  // to memory GLM(n) reads at its very end, so they are written only behind griddepcontrol.wait (GLM(n) complete).
+  pdl_launch_dependents();
   __shared__ double sh[2][256];
   const double phi = use_inline ? phi_inline : d_params[phi_index];
   double s_lg = 0.0, s_dg = 0.0;
@@ -480,6 +484,7 @@ __global__ void __launch_bounds__(256) nb_hist_sums_kernel(const unsigned int* _
     __syncthreads();
   }
   if (threadIdx.x == 0) {
+    pdl_wait();
     out[0] = sh[0][0];
     out[1] = sh[1][0];
   }
@@ -492,8 +497,19 @@ static int prepare_neg_binomial(const stan_cuda_data* d, const LaunchIO& io, Wor
   if (io.d_sigma_vec || !d->hist || io.d_y) return STAN_CUDA_OK;  // vector phi, outcomes too large for a histogram, or per-call outcomes
   double* out = ws->scratch + ws->scratch_doubles - 2;  // last two doubles of the workspace
   const bool inl = p->inline_n > 0;
-  nb_hist_sums_kernel<<<1, 256, 0, stream>>>(d->hist, d->hist_len, io.d_params, d->t.kpad + 1,
-                                             inl ? p->inline_params[d->t.kpad + 1] : 0.0, inl ? 1 : 0, out);
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1);
+    cfg.blockDim = dim3(256);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = p->pdl ? 1 : 0;
+    SC_CUDA(cudaLaunchKernelEx(&cfg, nb_hist_sums_kernel, static_cast<const unsigned int*>(d->hist), d->hist_len, io.d_params,
+                               d->t.kpad + 1, inl ? p->inline_params[d->t.kpad + 1] : 0.0, inl ? 1 : 0, out));
+  }
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   p->nb_sums = out;
@@ -540,17 +556,13 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   // not a column block, not next to other shards' launches).  A full-width grid then leaves `slack` CTA slots free:
   // the previous evaluation's last CTA may still sit in its exchange when this grid starts, and with a static tile
   // schedule a CTA that starts late finishes late.  STAN_CUDA_PDL=0 switches it off (A/B).
-  static const int pdl_on = [] {
-    const char* v = getenv("STAN_CUDA_PDL");
-    return v ? atoi(v) : 1;
-  }();
-  static const int pdl_slack = [] {
-    const char* v = getenv("STAN_CUDA_PDL_SLACK");
-    return v ? atoi(v) : 1;
-  }();
   const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
-  const bool pdl = pdl_on != 0 && !rowio && d->family <= STAN_CUDA_NORMAL_ID && !io.shared_gpu;
-  if (pdl && grid64 == int64_t(sms) * ctas_per_sm && grid64 > pdl_slack + 8) grid64 -= pdl_slack;
+  // neg_binomial_2_log qualifies on its histogram path (its pre-kernel joins the chain, prepare_neg_binomial);
+  // ordered_logistic as it is (class table and bins live in shared memory)
+  const bool nb_hist = d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG && !io.d_sigma_vec && d->hist && !io.d_y;
+  const bool pdl = pdl_enabled() && !rowio && !io.shared_gpu &&
+                   (d->family <= STAN_CUDA_NORMAL_ID || d->family == STAN_CUDA_ORDERED_LOGISTIC || nb_hist);
+  if (pdl && grid64 == int64_t(sms) * ctas_per_sm && grid64 > pdl_slack() + 8) grid64 -= pdl_slack();
   const int grid = int(grid64);
   int group_size = 1;
   while (group_size * group_size < grid) ++group_size;

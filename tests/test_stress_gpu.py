@@ -97,3 +97,73 @@ def test_many_shapes_stage_counts_and_grids(glm):
     finally:
         lib().stan_cuda_set_tuning(0, 0, 0)
     assert count == 200
+
+
+@pytest.mark.parametrize("family", ["neg_binomial_2_log", "ordered_logistic", "categorical_mma", "categorical_vector"])
+def test_back_to_back_launches_of_the_widened_families(glm, family):
+    """The same check for the families that joined the dependent-launch chain later: neg_binomial_2_log (whose
+    histogram pre-kernel sits between two GLM kernels and writes its two sums only after the previous evaluation
+    has completed), ordered_logistic and both categorical_logit kernels."""
+    import torch
+    from math_b200 import _abi
+    from math_b200._lib import lib
+    from tests.helpers import synth_categorical, synth_ordered
+    n, k, K = 300_007, 32, 30
+    ncls = 5
+    lib().stan_cuda_set_categorical_kernel(0 if family == "categorical_vector" else 1)
+    try:
+        if family == "neg_binomial_2_log":
+            s = synth_glm(family, n, k, seed=4)
+            data = glm.GlmData(s["family"], s["x"], s["y"])
+            flags = glm.glm_flags(s["family"], False)
+            plen, rlen = data.params_len, data.result_len
+        elif family == "ordered_logistic":
+            s = synth_ordered(n, k, ncls, seed=4)
+            data = glm.GlmData(_abi.ORDERED_LOGISTIC, s["x"], s["y"])
+            flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+            plen, rlen = data.params_len + ncls - 1, data.result_len + ncls - 1
+        else:
+            s = synth_categorical(n, k, ncls, seed=4)
+            data = glm.GlmData(_abi.CATEGORICAL_LOGIT, s["x"], s["y"])
+            flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA
+            plen = ncls * (data.kpad + 1)
+            rlen = 4 + plen
+        params = np.zeros((K, plen))
+        for i in range(K):
+            f = 1.0 + 0.01 * i
+            if family == "neg_binomial_2_log":
+                params[i, :k], params[i, data.kpad], params[i, data.kpad + 1] = s["beta"] * f, 0.3, 2.5 + 0.01 * i
+            elif family == "ordered_logistic":
+                params[i, :k] = s["beta"] * f
+                params[i, data.kpad + 2:] = s["cuts"] * f
+            else:
+                for c in range(ncls):
+                    params[i, c * data.kpad:c * data.kpad + k] = s["beta"][:, c] * f
+                params[i, ncls * data.kpad:] = s["alpha"] * f
+        d_params = torch.from_numpy(params).cuda()
+        d_res = torch.zeros((K, rlen), dtype=torch.float64, device="cuda")
+        d_alone = torch.zeros((K, rlen), dtype=torch.float64, device="cuda")
+        stream = torch.cuda.Stream()
+
+        def go(i, out):
+            if family == "neg_binomial_2_log":
+                data.launch(flags, d_params[i].data_ptr(), out[i].data_ptr(), stream.cuda_stream)
+            elif family == "ordered_logistic":
+                data.launch_ordered(flags, d_params[i].data_ptr(), ncls - 1, out[i].data_ptr(), stream.cuda_stream)
+            else:
+                data.launch_categorical(flags, d_params[i].data_ptr(), ncls, out[i].data_ptr(), stream.cuda_stream)
+        torch.cuda.synchronize()
+        for i in range(K):
+            go(i, d_alone)
+            stream.synchronize()
+        for rep in range(3):
+            d_res.zero_()
+            torch.cuda.synchronize()
+            for i in range(K):
+                go(i, d_res)
+            stream.synchronize()
+            assert torch.equal(d_res, d_alone), "%s: overlapping launches differ from launches run alone (rep %d)" % (family, rep)
+        assert torch.isfinite(d_res[:, 0]).all() and float(d_res[:, 0].abs().min()) > 0
+        data.close()
+    finally:
+        lib().stan_cuda_set_categorical_kernel(1)
