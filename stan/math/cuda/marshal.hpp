@@ -15,6 +15,7 @@
 #include <tbb/parallel_for.h>
 #include <tbb/task_arena.h>
 #endif
+#include <cstdlib>
 #include <memory>
 #include <type_traits>
 #include <vector>
@@ -33,13 +34,33 @@ namespace cuda {
  * (stan_cuda_host_staging is per thread) and leaving the shard scope of the outer job closed.  Isolation restricts
  * the waiting thread to tasks of this loop (test: map_rect_dispatch_mock_test.cpp, nested_parallel_gather_...).
  */
+/** How many workers share one of these passes (default 2, STAN_CUDA_HOST_PARTS).  Measured on the B200 hosts at
+ * N = 1e6 (profiles/r02_host_thread_sweep.txt): 2-3 workers are the optimum -- C1 6.2-6.4 ms against 6.8 ms serial,
+ * 6.9-7.3 ms with 4-6 and 9.3 ms with all 16 cores.  The passes stream 8-24 MB that ONE thread then walks again (the D2H copy into the
+ * partials, grad() over the tape, the caller reading the adjoints): spread over every core's private cache the
+ * data has to travel back line by line (device call 0.75 -> 1.56 ms, grad() 2.9 -> 5.2 ms with 16 workers). */
+inline size_t host_pass_parts() {
+  static const size_t parts = [] {
+    const char* v = std::getenv("STAN_CUDA_HOST_PARTS");
+    const long p = v ? std::atol(v) : 2;
+    return static_cast<size_t>(p < 1 ? 1 : (p > 64 ? 64 : p));
+  }();
+  return parts;
+}
+
 template <typename Body>
 inline void for_each_chunk(size_t n, const Body& body) {
 #ifdef STAN_THREADS
-  if (n >= (size_t(1) << 16)) {
+  const size_t parts = host_pass_parts();
+  if (n >= (size_t(1) << 16) && parts > 1) {
+    const size_t per = (n + parts - 1) / parts;
     tbb::this_task_arena::isolate([&] {
-      tbb::parallel_for(tbb::blocked_range<size_t>(0, n, size_t(1) << 15),
-                        [&](const tbb::blocked_range<size_t>& r) { body(r.begin(), r.end()); });
+      tbb::parallel_for(size_t(0), parts, [&](size_t q) {
+        const size_t begin = q * per, end = begin + per < n ? begin + per : n;
+        if (begin < end) {
+          body(begin, end);
+        }
+      });
     });
     return;
   }
