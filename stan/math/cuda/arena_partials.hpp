@@ -18,13 +18,16 @@ namespace cuda {
 template <typename T>
 struct operand_edge {
   static size_t size(const T& /*v*/) { return 0; }
-  static bool dump(const T& /*v*/, vari** /*dst*/) { return false; }
+  static bool dump(const T& /*v*/, vari** /*dst*/, double* /*vals*/ = nullptr) { return false; }
 };
 template <>
 struct operand_edge<var> {
   static size_t size(const var& /*v*/) { return 1; }
-  static bool dump(const var& v, vari** dst) {
+  static bool dump(const var& v, vari** dst, double* vals = nullptr) {
     dst[0] = v.vi_;
+    if (vals) {
+      vals[0] = v.vi_->val_;
+    }
     return false;
   }
 };
@@ -38,7 +41,9 @@ constexpr size_t bulk_chain_min = size_t(1) << 17;
  * updates of different elements never touch the same memory (it is what a vector of parameters built element after
  * element on the autodiff arena looks like).  Returns that answer (false for small edges: they keep the serial loop).
  */
-inline bool dump_var_array(const var* v, size_t n, vari** dst) {
+inline bool dump_var_array(const var* v, size_t n, vari** dst, double* vals = nullptr) {
+  // `vals` (optional): the same pass also gathers the operand values, e.g. straight into the page-locked staging
+  // area the device call uploads from -- one walk over the N varis instead of two
 #ifdef STAN_THREADS
   if (n >= bulk_chain_min) {
     std::atomic<bool> ascending(true);
@@ -48,6 +53,9 @@ inline bool dump_var_array(const var* v, size_t n, vari** dst) {
       for (size_t i = begin; i != end; ++i) {
         vari* p = v[i].vi_;
         dst[i] = p;
+        if (vals) {
+          vals[i] = p->val_;
+        }
         mine = mine && prev < reinterpret_cast<uintptr_t>(p);
         prev = reinterpret_cast<uintptr_t>(p);
       }
@@ -61,10 +69,21 @@ inline bool dump_var_array(const var* v, size_t n, vari** dst) {
   for_each_chunk(n, [&](size_t begin, size_t end) {
     for (size_t i = begin; i != end; ++i) {
       dst[i] = v[i].vi_;
+      if (vals) {
+        vals[i] = v[i].vi_->val_;
+      }
     }
   });
   return false;
 }
+
+/** true for the operand kinds whose values the tape-node assembly can gather on its way (containers of var) */
+template <typename T>
+struct gathered_by_node : std::false_type {};
+template <>
+struct gathered_by_node<std::vector<var>> : std::true_type {};
+template <int R, int C, int O, int MR, int MC>
+struct gathered_by_node<Eigen::Matrix<var, R, C, O, MR, MC>> : std::true_type {};
 
 /**
  * The reference's precomputed_gradients_vari (rev/core/precomputed_gradients.hpp:20-76) with the adjoint scatter of
@@ -112,13 +131,15 @@ class bulk_gradients_vari : public precomputed_gradients_vari {
 template <>
 struct operand_edge<std::vector<var>> {
   static size_t size(const std::vector<var>& v) { return v.size(); }
-  static bool dump(const std::vector<var>& v, vari** dst) { return dump_var_array(v.data(), v.size(), dst); }
+  static bool dump(const std::vector<var>& v, vari** dst, double* vals = nullptr) {
+    return dump_var_array(v.data(), v.size(), dst, vals);
+  }
 };
 template <int R, int C, int O, int MR, int MC>
 struct operand_edge<Eigen::Matrix<var, R, C, O, MR, MC>> {
   typedef Eigen::Matrix<var, R, C, O, MR, MC> T;
   static size_t size(const T& v) { return v.size(); }
-  static bool dump(const T& v, vari** dst) { return dump_var_array(v.data(), v.size(), dst); }
+  static bool dump(const T& v, vari** dst, double* vals = nullptr) { return dump_var_array(v.data(), v.size(), dst, vals); }
 };
 
 /**
@@ -138,7 +159,7 @@ template <typename T1, typename T2 = double, typename T3 = double, typename T4 =
 class arena_partials {
  public:
   explicit arena_partials(const T1& o1, const T2& o2 = T2(), const T3& o3 = T3(), const T4& o4 = T4(),
-                          const T5& o5 = T5()) {
+                          const T5& o5 = T5(), double* const* value_sinks = nullptr) {
     n_[0] = operand_edge<T1>::size(o1);
     n_[1] = operand_edge<T2>::size(o2);
     n_[2] = operand_edge<T3>::size(o3);
@@ -156,11 +177,12 @@ class arena_partials {
     if (off_[5] > 0) {
       varis_ = ChainableStack::instance_->memalloc_.alloc_array<vari*>(off_[5]);
       partials_ = ChainableStack::instance_->memalloc_.alloc_array<double>(off_[5]);
-      distinct_[0] = operand_edge<T1>::dump(o1, varis_ + off_[0]);
-      distinct_[1] = operand_edge<T2>::dump(o2, varis_ + off_[1]);
-      distinct_[2] = operand_edge<T3>::dump(o3, varis_ + off_[2]);
-      distinct_[3] = operand_edge<T4>::dump(o4, varis_ + off_[3]);
-      distinct_[4] = operand_edge<T5>::dump(o5, varis_ + off_[4]);
+      // value_sinks[e] (optional): where the values of edge e go in the same pass (gathered_by_node kinds only)
+      distinct_[0] = operand_edge<T1>::dump(o1, varis_ + off_[0], value_sinks ? value_sinks[0] : nullptr);
+      distinct_[1] = operand_edge<T2>::dump(o2, varis_ + off_[1], value_sinks ? value_sinks[1] : nullptr);
+      distinct_[2] = operand_edge<T3>::dump(o3, varis_ + off_[2], value_sinks ? value_sinks[2] : nullptr);
+      distinct_[3] = operand_edge<T4>::dump(o4, varis_ + off_[3], value_sinks ? value_sinks[3] : nullptr);
+      distinct_[4] = operand_edge<T5>::dump(o5, varis_ + off_[4], value_sinks ? value_sinks[4] : nullptr);
       for (int e = 0; e < 5; ++e) {  // small edges start from zero like operands_and_partials' (cheap insurance);
         if (n_[e] <= 4096) {         // an N-element edge is written entirely by the device
           zero(e);

@@ -39,23 +39,27 @@ inline const int* int_outcome_ptr(const Eigen::Matrix<int, R, C, O, MR, MC>& n) 
 }
 
 /** Fills the argument block shared by the two densities and calls the C ABI. */
+/** Page-locked staging for the operand's values (nullptr: the operand is borrowed, or the allocation failed -- the
+ * call then reports it). */
+template <typename T_prob>
+inline double* int_density_stage(const T_prob& theta) {
+  const size_t bt = staged_operand<T_prob>::bytes(theta);
+  return bt > 0 ? static_cast<double*>(stan_cuda_host_staging(bt)) : nullptr;
+}
+
 template <typename T_n, typename T_prob>
 inline int int_density_call(int density, bool lp_const, const T_n& n, const T_prob& theta, size_t N,
-                            arena_partials<T_prob>& ops_partials, double* logp) {
-  const size_t bt = staged_operand<T_prob>::bytes(theta);
-  double* stage = nullptr;
-  if (bt > 0) {
-    stage = static_cast<double*>(stan_cuda_host_staging(bt));
-    if (!stage) {
-      return STAN_CUDA_ERR_CUDA;
-    }
+                            arena_partials<T_prob>& ops_partials, double* stage, double* logp) {
+  if (staged_operand<T_prob>::bytes(theta) > 0 && !stage) {
+    return STAN_CUDA_ERR_CUDA;
   }
   stan_cuda_density_args a = stan_cuda_density_args();
   a.density = density;
   a.n = N;
   a.y = int_outcome_ptr(n);
   a.y_len = length(n);
-  a.theta = staged_operand<T_prob>::fill(theta, stage);
+  // (a container of var left its values in `stage` while the tape node was assembled: one pass over the operands)
+  a.theta = gathered_by_node<T_prob>::value ? stage : staged_operand<T_prob>::fill(theta, stage);
   a.theta_len = length(theta);
   a.lp = logp;
   a.flags = STAN_CUDA_LP_MAIN;
@@ -89,9 +93,11 @@ return_type_t<T_prob> bernoulli_logit_lpmf_device(const T_n& n, const T_prob& th
     check_consistent_sizes(function, "Random variable", n, "Probability parameter", theta);
     return 0.0;
   }
-  arena_partials<T_prob> ops_partials(theta);
+  double* const stage = int_density_stage(theta);
+  double* const sinks[5] = {gathered_by_node<T_prob>::value ? stage : nullptr, nullptr, nullptr, nullptr, nullptr};
+  arena_partials<T_prob> ops_partials(theta, double(), double(), double(), double(), sinks);
   double logp = 0;
-  const int rc = int_density_call(STAN_CUDA_DENSITY_BERNOULLI_LOGIT, false, n, theta, N, ops_partials, &logp);
+  const int rc = int_density_call(STAN_CUDA_DENSITY_BERNOULLI_LOGIT, false, n, theta, N, ops_partials, stage, &logp);
   check_cuda_rc(function, rc);
   if (rc == STAN_CUDA_BAD_OPERAND) {
     check_bounded(function, "n", n, 0, 1);
@@ -120,10 +126,12 @@ return_type_t<T_log_rate> poisson_log_lpmf_device(const T_n& n, const T_log_rate
     check_consistent_sizes(function, "Random variable", n, "Log rate parameter", alpha);
     return 0.0;
   }
-  arena_partials<T_log_rate> ops_partials(alpha);
+  double* const stage = int_density_stage(alpha);
+  double* const sinks[5] = {gathered_by_node<T_log_rate>::value ? stage : nullptr, nullptr, nullptr, nullptr, nullptr};
+  arena_partials<T_log_rate> ops_partials(alpha, double(), double(), double(), double(), sinks);
   double logp = 0;
   const int rc = int_density_call(STAN_CUDA_DENSITY_POISSON_LOG, include_summand<propto>::value, n, alpha, N,
-                                  ops_partials, &logp);
+                                  ops_partials, stage, &logp);
   check_cuda_rc(function, rc);
   if (rc == STAN_CUDA_BAD_OPERAND) {
     check_nonnegative(function, "Random variable", n);

@@ -90,7 +90,6 @@ return_type_t<T_y, T_loc, T_scale> normal_lpdf_device(const T_y& y, const T_loc&
     check_consistent_sizes(function, "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
   }
 
-  arena_partials<T_y, T_loc, T_scale> ops_partials(y, mu, sigma);  // operands_and_partials, built in place
   const size_t by = staged_operand<T_y>::bytes(y), bm = staged_operand<T_loc>::bytes(mu),
                bs = staged_operand<T_scale>::bytes(sigma);
   double* stage = nullptr;
@@ -100,15 +99,22 @@ return_type_t<T_y, T_loc, T_scale> normal_lpdf_device(const T_y& y, const T_loc&
       check_cuda_rc(function, STAN_CUDA_ERR_CUDA);
     }
   }
+  double* const stage_y = stage;
+  double* const stage_mu = stage ? stage + by / sizeof(double) : nullptr;
+  double* const stage_sigma = stage ? stage + (by + bm) / sizeof(double) : nullptr;
+  // operands_and_partials, built in place; containers of var leave their values in the staging area in the same pass
+  double* const sinks[5] = {gathered_by_node<T_y>::value ? stage_y : nullptr, gathered_by_node<T_loc>::value ? stage_mu : nullptr,
+                            gathered_by_node<T_scale>::value ? stage_sigma : nullptr, nullptr, nullptr};
+  arena_partials<T_y, T_loc, T_scale> ops_partials(y, mu, sigma, double(), double(), sinks);
   double logp = 0;
   stan_cuda_normal_args a = stan_cuda_normal_args();
   a.n = N;
-  a.y = staged_operand<T_y>::fill(y, stage);
+  a.y = gathered_by_node<T_y>::value ? stage_y : staged_operand<T_y>::fill(y, stage_y);
   a.y_len = length(y);
   a.y_is_data = (is_constant_all<T_y>::value && staged_operand<T_y>::borrowed) ? 1 : 0;
-  a.mu = staged_operand<T_loc>::fill(mu, stage + by / sizeof(double));
+  a.mu = gathered_by_node<T_loc>::value ? stage_mu : staged_operand<T_loc>::fill(mu, stage_mu);
   a.mu_len = length(mu);
-  a.sigma = staged_operand<T_scale>::fill(sigma, stage + (by + bm) / sizeof(double));
+  a.sigma = gathered_by_node<T_scale>::value ? stage_sigma : staged_operand<T_scale>::fill(sigma, stage_sigma);
   a.sigma_len = length(sigma);
   a.lp = &logp;
   a.flags = STAN_CUDA_LP_MAIN;
