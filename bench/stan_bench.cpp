@@ -253,6 +253,23 @@ struct shard_functor_view {
   }
 };
 
+// What the unmodified functor does BEFORE it calls the GLM, and nothing else: the copy of x_r into a matrix and of the
+// outcomes into a vector.  Timed through the same map_rect to show how much of `gpu_map_rect` is this user code.
+struct shard_functor_copy_only {
+  template <typename T1, typename T2>
+  Matrix<typename stan::return_type<T1, T2>::type, Dynamic, 1> operator()(
+      const Matrix<T1, Dynamic, 1>& shared, const Matrix<T2, Dynamic, 1>& job, const std::vector<double>& x_r,
+      const std::vector<int>& x_i, std::ostream* msgs = 0) const {
+    typedef typename stan::return_type<T1, T2>::type T;
+    const int rows = x_i[0], k = x_i[1];
+    MatrixXd x = Eigen::Map<const MatrixXd>(x_r.data(), rows, k);
+    std::vector<int> y(x_i.begin() + 2, x_i.end());
+    Matrix<T, Dynamic, 1> res(1);
+    res(0) = job[0] * (x(rows - 1, k - 1) + double(y[rows - 1])) + shared[0] * x(0, 0);  // keeps both copies alive
+    return res;
+  }
+};
+
 struct ShardSet {
   std::vector<std::vector<double>> x_r;
   std::vector<std::vector<int>> x_i;
@@ -306,6 +323,8 @@ double map_rect_once(const Problem& p, const ShardSet& s, Result* out) {
     res = map_rect<CALL_ID, shard_functor<true, FAMILY, SHARED_ALPHA>>(shared, job, s.x_r, s.x_i);
   } else if (MODE == 2) {
     res = map_rect<CALL_ID + 200, shard_functor_view>(shared, job, s.x_r, s.x_i);
+  } else if (MODE == 3) {
+    res = map_rect<CALL_ID + 300, shard_functor_copy_only>(shared, job, s.x_r, s.x_i);
   } else {
     res = internal::map_rect_concurrent_reference_cpu<CALL_ID + 100, shard_functor<false, FAMILY, SHARED_ALPHA>>(
         shared, job, s.x_r, s.x_i, nullptr);
@@ -505,6 +524,10 @@ int run(int argc, char** argv) {
       std::printf(", ");
       print_timing("gpu_map_rect_zero_copy_view", tv);
       std::printf(", \"view_vs_copy_rel_err\": %.3e, ", rel_err(gv, g));
+      Result gc;
+      Timing tcp = time_reps(3, reps, 60, [&] { return map_rect_once<3, 0, false, 5>(p, s, &gc); });
+      print_timing("functor_copies_only_no_glm", tcp);
+      std::printf(", ");
     }
     if (!no_cpu) {
       Timing tc = time_reps(1, cpu_reps, 60, [&] { return map_rect_once<1, 0, false, 5>(p, s, &c); });

@@ -187,14 +187,30 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
       } else if ((p.flags & STAN_CUDA_NEED_DCUTS) && ncuts > 0) {
         // many classes: one owner lane per row adds into this warp's bins, rows in order, so the sum is
         // the same on every run (no floating-point atomics)
+        // Rows of the warp that hit the same bin are found with match.any; every member adds the group's values in
+        // lane order (so the sum does not depend on timing) and the lowest lane of the group makes the one update of
+        // that bin.  Two rounds -- all +d2 terms, then all -d1 terms (:192-200) -- instead of one predicated
+        // read-modify-write per row of the warp (32 serial steps at K = 32: 1e6 x 32 x 64 classes 73.9 -> see profiles).
         double* bins = red + size_t(warp) * cols + kpad + 4;
-        for (int r = 0; r < (PAIR ? 2 : 1) * rpw; ++r) {
-          if (rl == (PAIR ? r >> 1 : r) && (!PAIR || u == (r & 1)) && own && valid) {
-            if (c != ncuts + 1) bins[c - 1] += o.t3;
-            if (c != 1) bins[c - 2] -= o.t2;
+        auto bin_add = [&](bool active, int key, double val) {
+          const int mykey = active ? key : -1 - lane;  // inactive lanes form groups of their own
+          const unsigned grp = __match_any_sync(0xffffffffu, mykey);
+          unsigned rem = grp;
+          double acc = 0.0;
+          while (__any_sync(0xffffffffu, rem != 0u)) {
+            const int src = rem ? __ffs(rem) - 1 : lane;
+            const double v = __shfl_sync(0xffffffffu, val, src);
+            if (rem) {
+              acc += v;
+              rem &= rem - 1;
+            }
           }
+          if (active && lane == __ffs(grp) - 1) bins[key] += acc;
           __syncwarp();
-        }
+        };
+        const bool mine = own && valid;
+        bin_add(mine && c != ncuts + 1, c - 1, o.t3);
+        bin_add(mine && c != 1, c - 2, -o.t2);
       }
     } else if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
       o = nb_row_epilogue(eta, alpha, yv, sigma_row, log_sigma_row, inv_sigma, p.flags, ROWIO && p.nb_rowfun != 0, ROWIO);
