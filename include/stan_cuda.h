@@ -337,8 +337,8 @@ STAN_CUDA_API int stan_cuda_glm_launch_categorical(stan_cuda_data_t d, uint32_t 
  * intercept / scale (no per-row operands, no collective), but the call allocates NOTHING: the reduction scratch of
  * the kernel (per-CTA partials, group sums, ticket words) lives in a file-scope __device__ array of the library,
  * 320 x 520 doubles = 1.27 MiB (+ 256 B of tickets) that every GPU which loads the library holds until exit.
- * Limit: (CTAs + reduction groups) x (k_pad + 4) + 2 <= 166400 doubles, i.e. every k <= 512 on a GPU of up to
- * 160 SMs; beyond it the call returns STAN_CUDA_ERR_ARG with the two numbers in stan_cuda_last_error().
+ * Limit: (CTAs + reduction groups) x (k_pad + 4) + 2 <= 166400 doubles, i.e. every k <= 512 (one warp tile; wider
+ * matrices run as several launches and are not served here) on a GPU of up to 160 SMs; beyond it the call returns STAN_CUDA_ERR_ARG with the two numbers in stan_cuda_last_error().
  * Every call on a device shares that one array: calls that OVERLAP on a GPU (two streams, two host threads) race
  * on it -- the caller serialises them.  The data handle, d_params and d_result are the caller's (created before
  * the no-allocation region); the first call per device resolves the array's device address (cudaGetSymbolAddress),

@@ -873,6 +873,9 @@ extern "C" int stan_cuda_glm_launch_noalloc(stan_cuda_data_t d, uint32_t flags, 
   if (!d || !d_params || !d_result) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: null argument");
   if (d->family > STAN_CUDA_NORMAL_ID)
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: bernoulli_logit, poisson_log and normal_id only");
+  if (!d->colblocks.empty())
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: k <= 512 only (a wider matrix is evaluated as several launches "
+                                   "with per-row temporaries in an allocated workspace)");
   if (d->t.layout != kLayoutWarp)
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_launch_noalloc: the data block was created for another kernel variant");
   if (flags & STAN_CUDA_FUSED_ALLREDUCE)

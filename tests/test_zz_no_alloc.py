@@ -80,3 +80,10 @@ def test_noalloc_launch_rejects_what_it_cannot_serve():
     finally:
         data.close()
     assert lib().stan_cuda_glm_launch_noalloc(None, 0, None, None, None) == _abi.ERR_ARG
+    s = synth_glm("poisson_log", 300, 600, seed=3)      # wider than one warp tile: several launches, not served here
+    data = glm.GlmData(s["family"], s["x"], s["y"])
+    try:
+        rc = lib().stan_cuda_glm_launch_noalloc(data.h, glm.glm_flags(s["family"], False), 8, 8, None)
+        assert rc == _abi.ERR_ARG and b"512" in lib().stan_cuda_last_error()
+    finally:
+        data.close()
