@@ -343,6 +343,19 @@ static int check_glm_args(const stan_cuda_glm_args* a) {
   return STAN_CUDA_OK;
 }
 
+// How long the host spins on the completion flag before it hands the wait to the driver.  Round 1 gave up after 250 us,
+// so every evaluation longer than that (C3: 1.4 ms) paid a blocking cudaStreamSynchronize and its wake-up latency on top
+// of the kernel.  A sampler's thread has nothing else to do until the gradient is there: spin for up to 50 ms
+// (STAN_CUDA_SPIN_US), then fall back (a faulted kernel never raises the flag; the driver call then reports the error).
+static int64_t spin_limit_us() {
+  static const int64_t us = [] {
+    const char* v = getenv("STAN_CUDA_SPIN_US");
+    const long long x = v ? atoll(v) : 50000;
+    return int64_t(x < 0 ? 0 : x);
+  }();
+  return us;
+}
+
 static bool low_latency_enabled() {
   static const bool on = [] {
     const char* v = getenv("STAN_CUDA_LOW_LATENCY");
@@ -562,7 +575,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
       int spins = 0;
       while (*flag != td->host_seq) {
         if ((++spins & 1023) == 0 &&
-            std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(250)) {
+            std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(spin_limit_us())) {
           // long kernel (or a fault): let the driver block / report
           SC_CUDA(cudaSetDevice(e->shards[s].d->device));
           SC_CUDA(cudaStreamSynchronize(td->stream));
