@@ -232,6 +232,26 @@ TEST(CudaGlmVariants, var_design_matrix) {
   }
 }
 
+TEST(CudaGlmVariants, scalar_weight_broadcast_over_several_columns) {
+  // a scalar beta passes check_consistent_size for any number of columns; the device path broadcasts it and sums the K
+  // gradient components into its ONE partials slot (round 1 copied K doubles over that slot: advisor finding)
+  Problem p = make_problem(301, 7, 21);
+  using namespace stan::math;  // NOLINT
+  var alpha = 0.3, b = 0.11;
+  var lp = poisson_log_glm_lpmf(p.y_pois, p.x, alpha, b);
+  lp.grad();
+  const double v = lp.val(), gb = b.adj(), ga = alpha.adj();
+  set_zero_all_adjoints();
+  vector_v beta = to_v(VectorXd::Constant(7, 0.11));
+  var alpha2 = 0.3;
+  var lp2 = poisson_log_glm_lpmf_reference_cpu(p.y_pois, p.x, alpha2, beta);
+  lp2.grad();
+  expect_rel(v, lp2.val(), std::fabs(lp2.val()), "scalar beta value");
+  expect_rel(gb, adj(beta).sum(), std::fabs(adj(beta).sum()), "scalar beta gradient = sum of the components");
+  expect_rel(ga, alpha2.adj(), std::fabs(alpha2.adj()), "alpha gradient");
+  stan::math::recover_memory();
+}
+
 TEST(CudaGlmVariants, ordered_logistic) {
   using stan::math::ordered_logistic_glm_lpmf;
   using stan::math::ordered_logistic_glm_lpmf_reference_cpu;
