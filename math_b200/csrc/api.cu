@@ -279,6 +279,7 @@ static int get_glm_entry(const stan_cuda_glm_args* a, std::shared_ptr<Entry>* ou
     return STAN_CUDA_OK;
   }
   counters().cache_misses.fetch_add(1, std::memory_order_relaxed);
+  NvtxRange fill_range("stan_cuda cache fill (upload + re-tiling)");
   if (it != g_cache.end()) g_cache.erase(it);  // stale: same identity, different content
   make_room_locked(a->n * ((a->k + 15) / 16 * 16 + 1) * int64_t(sizeof(double)));  // tiled x (padded) + y
   auto t0 = std::chrono::steady_clock::now();
@@ -374,6 +375,7 @@ struct ShardRun {
 };
 
 int glm_eval(const stan_cuda_glm_args* a) {
+  NvtxRange range("stan_cuda_glm_eval");
   SC_TRY(check_glm_args(a));
   if (a->n == 0) {  // size_zero(y): the reference returns 0 before touching anything (:72-74)
     if (a->lp) *a->lp = 0.0;
@@ -567,6 +569,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
     SC_TRY(comm_allreduce_rank(runs[0].d_result, int64_t(nr), runs[0].td->stream));
   }
   // results back
+  NvtxRange wait_range("stan_cuda wait for the result block");
   if (low_latency) {
     for (size_t s = 0; s < S; ++s) {
       ThreadDev* td = runs[s].td;
@@ -657,6 +660,7 @@ int glm_eval(const stan_cuda_glm_args* a) {
 namespace stancuda {
 
 int glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int* item_rc) {
+  NvtxRange range("stan_cuda_glm_eval_batch");
   if (!items || count < 1) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval_batch: no items");
   const int family = items[0].family;
   if (family < STAN_CUDA_BERNOULLI_LOGIT || family > STAN_CUDA_NORMAL_ID)
@@ -838,6 +842,7 @@ static int get_vec_entry(const double* v, int64_t n, int device, cudaStream_t st
 }
 
 int normal_lpdf_eval(const stan_cuda_normal_args* a) {
+  NvtxRange range("stan_cuda_normal_lpdf_eval");
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: null args");
   if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: negative n");
   if (a->n == 0) {  // size_zero(y, mu, sigma) -> 0 (normal_lpdf.hpp:45-47)
@@ -960,6 +965,7 @@ static int get_ivec_entry(const int32_t* v, int64_t n, int device, int want_lgam
 }
 
 int density_eval(const stan_cuda_density_args* a) {
+  NvtxRange range("stan_cuda_density_eval");
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: null args");
   if (a->density != STAN_CUDA_DENSITY_BERNOULLI_LOGIT && a->density != STAN_CUDA_DENSITY_POISSON_LOG)
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: unknown density");

@@ -210,6 +210,7 @@ PeerXchg* comm_local_xchg(const std::vector<int>& devices) {
 int comm_world_size() { return g_world; }
 
 int comm_allreduce_rank(double* d_buf, int64_t count, cudaStream_t stream) {
+  NvtxRange range("stan_cuda ncclAllReduce (result block)");
   if (!g_rank_comm) return fail(STAN_CUDA_ERR_STATE, "no multi-process communicator (stan_cuda_comm_init_rank)");
   int rc = g_api.AllReduce(d_buf, d_buf, size_t(count), ncclFloat64, ncclSum, g_rank_comm, stream);
   if (rc != ncclSuccess) return fail_nccl(rc, "ncclAllReduce");

@@ -11,7 +11,17 @@
 
 #include "../../include/stan_cuda.h"
 
+#include <nvtx3/nvToolsExt.h>  // header-only (NVTX v3): ranges are no-ops unless a profiler is attached
+
 namespace stancuda {
+
+// NVTX range for the duration of a scope (upload / evaluation / exchange ranges for nsys / ncu timelines)
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // ---- error plumbing: no exception leaves the library, text goes to a thread-local string ----
 void set_last_error(const std::string& s);

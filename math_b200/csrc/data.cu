@@ -173,6 +173,7 @@ static const size_t kStageBytes = size_t(256) << 20;  // staging buffer for the 
 // Upload rows [row0, row0 + d->n) of the host matrix into d (already sized; d->t chosen).
 int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_major, const void* y,
                     int64_t row0, cudaStream_t stream, uint64_t* bytes_uploaded) {
+  NvtxRange range("stan_cuda upload_glm_data");
   const Tiling& t = d->t;
   const int64_t n = d->n, k = d->k;
   SC_CUDA(cudaSetDevice(d->device));
