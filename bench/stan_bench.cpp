@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|s1|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -360,6 +360,28 @@ double normal_once(const VectorXd& y, const VectorXd& mu_val, double sigma_val, 
   return t1 - t0;
 }
 
+// student_t_lpdf as a model states it -- data y, var nu, var vector mu, var sigma; one evaluation =
+// forward + grad() + reading the N + 2 adjoints
+template <bool GPU>
+double student_t_once(const VectorXd& y, double nu_val, const VectorXd& mu_val, double sigma_val, Result* out) {
+  using namespace stan::math;  // NOLINT
+  start_nested();
+  vector_v mu(mu_val.size());
+  for (int64_t i = 0; i < mu_val.size(); ++i) mu[i] = mu_val[i];
+  var nu = nu_val, sigma = sigma_val;
+  const double t0 = now();
+  var lp = GPU ? student_t_lpdf(y, nu, mu, sigma) : student_t_lpdf_reference_cpu<false>(y, nu, mu, sigma);
+  grad(lp.vi_);
+  out->lp = lp.val();
+  out->grad.resize(mu.size() + 2);
+  for (int64_t i = 0; i < mu.size(); ++i) out->grad[i] = mu[i].adj();
+  out->grad[mu.size()] = sigma.adj();
+  out->grad[mu.size() + 1] = nu.adj();
+  const double t1 = now();
+  recover_memory_nested();
+  return t1 - t0;
+}
+
 // vectorised lpmf with an integer outcome and a var vector operand (DENSITY 1: bernoulli_logit_lpmf,
 // 2: poisson_log_lpmf); one evaluation = forward + grad() + reading the N adjoints
 template <bool GPU, int DENSITY>
@@ -467,6 +489,29 @@ int run(int argc, char** argv) {
     print_timing("gpu", tg);
     if (!no_cpu) {
       Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, [&] { return normal_once<false>(y, mu, 1.3, &c); });
+      std::printf(", ");
+      print_timing("cpu_reference_1_thread", tc);
+      std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
+    }
+    std::printf(", \"algorithmic_device_bytes\": %lld}\n", (long long)(3 * n * 8));
+    return 0;
+  }
+
+  if (config == "s1") {
+    const int64_t n = n_override ? n_override : 1000000;
+    VectorXd y(n), mu(n);
+    Rng r(1021);
+    for (int64_t i = 0; i < n; ++i) {
+      y[i] = 1.5 * r.normal();
+      mu[i] = 0.1 * r.normal();
+    }
+    Result g, c;
+    student_t_once<true>(y, 4.0, mu, 1.3, &g);
+    Timing tg = time_reps(3, reps, 30, [&] { return student_t_once<true>(y, 4.0, mu, 1.3, &g); });
+    std::printf("\"what\": \"student_t_lpdf N=%lld, y data, nu var, mu var vector, sigma var\", ", (long long)n);
+    print_timing("gpu", tg);
+    if (!no_cpu) {
+      Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, [&] { return student_t_once<false>(y, 4.0, mu, 1.3, &c); });
       std::printf(", ");
       print_timing("cpu_reference_1_thread", tc);
       std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));

@@ -22,6 +22,7 @@
  *                                device; the per-job loop of
  *                                  stan/math/rev/mat/functor/map_rect_concurrent.hpp:39-54
  *   stan_cuda_normal_lpdf_eval   the loop of normal_lpdf      stan/math/prim/scal/prob/normal_lpdf.hpp:67-110
+ *   stan_cuda_student_t_lpdf_eval the loops of student_t_lpdf stan/math/prim/scal/prob/student_t_lpdf.hpp:85-199
  *   stan_cuda_density_eval       the loops of the vectorised elementwise densities
  *                                  bernoulli_logit_lpmf      stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
  *                                  poisson_log_lpmf          stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93
@@ -197,6 +198,36 @@ typedef struct stan_cuda_density_args {
   double* dtheta;       /* [theta_len]: per element, or the sum over n for a scalar operand */
 } stan_cuda_density_args;
 
+/* student_t_lpdf(y | nu, mu, sigma), vectorised over any mix of scalar / length-n operands: value and the
+ * partials of all four operands in one pass (stan/math/prim/scal/prob/student_t_lpdf.hpp:55-201).
+ * The summands the reference drops under propto (:117-146) are selected by flags:
+ *   STAN_CUDA_LP_CONST  NEG_LOG_SQRT_PI per element                                              (:134-136)
+ *   STAN_CUDA_LP_DOF    lgamma(nu/2 + 1/2) - lgamma(nu/2) - log(nu)/2                            (:137-140)
+ *   STAN_CUDA_LP_SCALE  -log(sigma)                                                              (:141-143)
+ *   STAN_CUDA_LP_MAIN   -(nu/2 + 1/2) * log1p(((y - mu) / sigma)^2 / nu)                         (:144-147)
+ * Partials are written per element for a length-n operand and as the sum over n for a scalar one. */
+#define STAN_CUDA_LP_DOF 0x800u
+#define STAN_CUDA_NEED_DNU 0x08u /* shares the bit of NEED_DBETA */
+
+typedef struct stan_cuda_student_t_args {
+  uint32_t flags;      /* STAN_CUDA_LP_{CONST,DOF,SCALE,MAIN} | NEED_DY | NEED_DNU | NEED_DALPHA (= d/dmu) | NEED_DSIGMA */
+  int32_t y_is_data;   /* 1: y is immutable data, cached on the device; 0: uploaded every call */
+  int64_t n;           /* max_size(y, nu, mu, sigma) */
+  const double* y;
+  int64_t y_len;       /* 1 or n */
+  const double* nu;
+  int64_t nu_len;      /* 1 or n */
+  const double* mu;
+  int64_t mu_len;      /* 1 or n */
+  const double* sigma;
+  int64_t sigma_len;   /* 1 or n */
+  double* lp;          /* [1] */
+  double* dy;          /* [y_len] */
+  double* dnu;         /* [nu_len] */
+  double* dmu;         /* [mu_len] */
+  double* dsigma;      /* [sigma_len] */
+} stan_cuda_student_t_args;
+
 typedef struct stan_cuda_stats_t {
   uint64_t cache_hits;
   uint64_t cache_misses;
@@ -254,6 +285,10 @@ STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
  * (:43 / :39) -- every element is tested inside the kernel, the wrapper then runs the reference's own checks
  * to throw the identical exception -- and STAN_CUDA_LOG_ZERO as described above. */
 STAN_CUDA_API int stan_cuda_density_eval(const stan_cuda_density_args* a);
+/* Returns STAN_CUDA_BAD_OPERAND when y is NaN, nu or sigma is not positive and finite, or mu is not finite
+ * (student_t_lpdf.hpp:67-70; tested per element inside the kernel, the wrapper then runs the reference's own
+ * checks to throw the identical exception). */
+STAN_CUDA_API int stan_cuda_student_t_lpdf_eval(const stan_cuda_student_t_args* a);
 /* Page-locked staging memory of the calling thread (at least `bytes`, valid until the thread's next
  * call with a larger size).  Operands gathered into it upload by DMA without a bounce buffer. */
 STAN_CUDA_API void* stan_cuda_host_staging(size_t bytes);

@@ -10,7 +10,7 @@ from ._abi import (BERNOULLI_LOGIT, NORMAL_ID, POISSON_LOG, LP_ALL, LP_CONST, LP
 
 def __getattr__(name):
     # lazy: importing the package must not need the built library
-    if name in ("bernoulli_logit_glm_lpmf", "poisson_log_glm_lpmf", "normal_id_glm_lpdf", "neg_binomial_2_log_glm_lpmf", "normal_lpdf",
+    if name in ("bernoulli_logit_glm_lpmf", "poisson_log_glm_lpmf", "normal_id_glm_lpdf", "neg_binomial_2_log_glm_lpmf", "normal_lpdf", "student_t_lpdf",
                 "GlmData", "glm_eval", "init", "init_device", "describe", "stats", "cache_clear",
                 "cache_invalidate", "shard_scope", "DomainError", "comm_init_from_torch"):
         from . import glm

@@ -21,6 +21,8 @@ LP_LINEAR = 0x200
 NEED_DBETA, NEED_DALPHA, NEED_DSIGMA, NEED_DY, NEED_ALL = 0x08, 0x10, 0x20, 0x40, 0x78
 NEED_DCUTS = 0x20
 NEED_DX = 0x400
+LP_DOF = 0x800      # student_t_lpdf: lgamma(nu/2 + 1/2) - lgamma(nu/2) - log(nu)/2
+NEED_DNU = 0x08     # student_t_lpdf: d/dnu (shares the bit of NEED_DBETA)
 FUSED_ALLREDUCE = 0x100
 
 c_double_p = C.POINTER(C.c_double)
@@ -77,6 +79,27 @@ class NormalArgs(C.Structure):
     ]
 
 
+class StudentTArgs(C.Structure):
+    _fields_ = [
+        ("flags", C.c_uint32),
+        ("y_is_data", C.c_int32),
+        ("n", C.c_int64),
+        ("y", C.c_void_p),
+        ("y_len", C.c_int64),
+        ("nu", C.c_void_p),
+        ("nu_len", C.c_int64),
+        ("mu", C.c_void_p),
+        ("mu_len", C.c_int64),
+        ("sigma", C.c_void_p),
+        ("sigma_len", C.c_int64),
+        ("lp", C.c_void_p),
+        ("dy", C.c_void_p),
+        ("dnu", C.c_void_p),
+        ("dmu", C.c_void_p),
+        ("dsigma", C.c_void_p),
+    ]
+
+
 DENSITY_BERNOULLI_LOGIT, DENSITY_POISSON_LOG = 1, 2
 DENSITIES = {"bernoulli_logit": DENSITY_BERNOULLI_LOGIT, "poisson_log": DENSITY_POISSON_LOG}
 
@@ -126,6 +149,7 @@ PROTOTYPES = {
     "stan_cuda_glm_eval_batch": (C.c_int, [C.POINTER(GlmArgs), C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "stan_cuda_density_eval": (C.c_int, [C.POINTER(DensityArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
+    "stan_cuda_student_t_lpdf_eval": (C.c_int, [C.POINTER(StudentTArgs)]),
     "stan_cuda_host_staging": (C.c_void_p, [C.c_size_t]),
     "stan_cuda_cache_invalidate": (C.c_int, [C.c_void_p]),
     "stan_cuda_cache_clear": (None, []),

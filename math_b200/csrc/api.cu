@@ -918,6 +918,80 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+// student_t_lpdf (student_t.cu): the four operands travel like those of normal_lpdf -- a length-n data y is cached
+// on the device, every other vector is uploaded per call, scalars go by value
+int student_t_lpdf_eval(const stan_cuda_student_t_args* a) {
+  NvtxRange range("stan_cuda_student_t_lpdf_eval");
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_student_t_lpdf_eval: null args");
+  if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_student_t_lpdf_eval: negative n");
+  if (a->n == 0) {  // size_zero(y, nu, mu, sigma) -> 0 (student_t_lpdf.hpp:57-59)
+    if (a->lp) *a->lp = 0.0;
+    return STAN_CUDA_OK;
+  }
+  if (!a->y || !a->nu || !a->mu || !a->sigma) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_student_t_lpdf_eval: null operand");
+  const int64_t n = a->n;
+  const double* src[4] = {a->y, a->nu, a->mu, a->sigma};
+  const int64_t len[4] = {a->y_len, a->nu_len, a->mu_len, a->sigma_len};
+  double* grad[4] = {a->dy, a->dnu, a->dmu, a->dsigma};
+  const uint32_t need_bit[4] = {STAN_CUDA_NEED_DY, STAN_CUDA_NEED_DNU, STAN_CUDA_NEED_DALPHA, STAN_CUDA_NEED_DSIGMA};
+  for (int q = 0; q < 4; ++q)
+    if (len[q] != 1 && len[q] != n) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_student_t_lpdf_eval: operand length must be 1 or n");
+  SC_TRY(ensure_init());
+  Context& c = context();
+  const int dev = tl_scope.active ? c.devices[size_t(tl_scope.device) % c.devices.size()] : c.devices[0];
+  ThreadDev* td;
+  SC_TRY(thread_dev(dev, &td));
+  SC_CUDA(cudaSetDevice(dev));
+  bool vec[4], need[4];
+  uint32_t flags = a->flags & ~uint32_t(STAN_CUDA_NEED_DY | STAN_CUDA_NEED_DNU | STAN_CUDA_NEED_DALPHA | STAN_CUDA_NEED_DSIGMA);
+  for (int q = 0; q < 4; ++q) {
+    vec[q] = len[q] != 1;
+    need[q] = (a->flags & need_bit[q]) && grad[q];
+    if (need[q]) flags |= need_bit[q];
+  }
+  std::shared_ptr<Entry> ycache;
+  if (vec[0] && a->y_is_data) SC_TRY(get_vec_entry(a->y, n, dev, td->stream, &ycache));
+  const size_t nal = (size_t(n) + 1) & ~size_t(1);
+  size_t want = 8;
+  for (int q = 0; q < 4; ++q) {
+    if (vec[q] && !(q == 0 && ycache)) want += nal;
+    if (vec[q] && need[q]) want += nal;
+  }
+  SC_TRY(td->reserve_dev(want));
+  SC_TRY(td->reserve_host(8));
+  double* p = td->d_buf;
+  StudentTIO io{};
+  io.flags = flags;
+  io.n = n;
+  io.result = p; p += 8;
+  io.y0 = a->y[0]; io.nu0 = a->nu[0]; io.mu0 = a->mu[0]; io.sigma0 = a->sigma[0];
+  const double** in_slot[4] = {&io.y, &io.nu, &io.mu, &io.sigma};
+  double** out_slot[4] = {&io.dy_row, &io.dnu_row, &io.dmu_row, &io.dsigma_row};
+  for (int q = 0; q < 4; ++q) {
+    if (!vec[q]) continue;
+    if (q == 0 && ycache) {
+      io.y = ycache->vec;
+      continue;
+    }
+    SC_CUDA(cudaMemcpyAsync(p, src[q], size_t(n) * sizeof(double), cudaMemcpyHostToDevice, td->stream));
+    *in_slot[q] = p; p += nal;
+  }
+  for (int q = 0; q < 4; ++q)
+    if (vec[q] && need[q]) { *out_slot[q] = p; p += nal; }
+  SC_TRY(launch_student_t_lpdf(io, &td->ws, dev, td->stream));
+  SC_CUDA(cudaMemcpyAsync(td->h_pinned, io.result, 8 * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  for (int q = 0; q < 4; ++q)
+    if (*out_slot[q]) SC_CUDA(cudaMemcpyAsync(grad[q], *out_slot[q], size_t(n) * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  SC_CUDA(cudaStreamSynchronize(td->stream));
+  const double* res = td->h_pinned;
+  if (a->lp) *a->lp = res[0];
+  for (int q = 0; q < 4; ++q)
+    if (need[q] && !vec[q]) grad[q][0] = res[1 + q];
+  counters().evals.fetch_add(1, std::memory_order_relaxed);
+  if (res[6] != 0.0) return STAN_CUDA_BAD_OPERAND;
+  return isfinite(res[5]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
 // =============================================================================================
 // vectorised elementwise densities (density.cu)
 // =============================================================================================
@@ -1068,6 +1142,7 @@ int stan_cuda_glm_eval_batch(const stan_cuda_glm_args* items, int count, int cal
   return glm_eval_batch(items, count, call_id, item_rc);
 }
 int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) { return normal_lpdf_eval(a); }
+int stan_cuda_student_t_lpdf_eval(const stan_cuda_student_t_args* a) { return student_t_lpdf_eval(a); }
 int stan_cuda_density_eval(const stan_cuda_density_args* a) { return density_eval(a); }
 void* stan_cuda_host_staging(size_t bytes) { return host_staging(bytes); }
 

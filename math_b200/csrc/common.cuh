@@ -198,6 +198,17 @@ struct NormalIO {
 };
 int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream_t stream);
 
+// student_t_lpdf kernel (student_t.cu)
+struct StudentTIO {
+  uint32_t flags;
+  int64_t n;
+  const double* y; const double* nu; const double* mu; const double* sigma;  // device vectors, or null for a scalar operand
+  double y0, nu0, mu0, sigma0;                                              // scalar operands by value
+  double* dy_row; double* dnu_row; double* dmu_row; double* dsigma_row;     // per-element outputs (vector operands) or null
+  double* result;  // [8]: lp, sum dy, sum dnu, sum dmu, sum dsigma, witness, bad-operand bits, 0
+};
+int launch_student_t_lpdf(const StudentTIO& io, Workspace* ws, int device, cudaStream_t stream);
+
 // vectorised elementwise densities (density.cu)
 struct DensityIO {
   int density;

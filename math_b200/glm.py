@@ -434,6 +434,74 @@ def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
     return float(lp[0]), grads
 
 
+def student_t_eval(y, nu, mu, sigma, flags, y_is_data=True):
+    """One stan_cuda_student_t_lpdf_eval call; returns {"rc", "lp", "dy", "dnu", "dmu", "dsigma"} (partials for the
+    NEED_* bits in flags, each the length of its operand)."""
+    ops = [_f64(v) for v in (y, nu, mu, sigma)]
+    n = max(o.size for o in ops) if min(o.size for o in ops) > 0 else 0
+    lp = np.zeros(1)
+    grads = [np.zeros(max(o.size, 1)) for o in ops]
+    a = _abi.StudentTArgs()
+    a.flags, a.y_is_data, a.n = flags, int(y_is_data), n
+    a.y, a.y_len, a.nu, a.nu_len = ops[0].ctypes.data, ops[0].size, ops[1].ctypes.data, ops[1].size
+    a.mu, a.mu_len, a.sigma, a.sigma_len = ops[2].ctypes.data, ops[2].size, ops[3].ctypes.data, ops[3].size
+    a.lp, a.dy, a.dnu, a.dmu, a.dsigma = (lp.ctypes.data, grads[0].ctypes.data, grads[1].ctypes.data,
+                                          grads[2].ctypes.data, grads[3].ctypes.data)
+    rc = check(lib().stan_cuda_student_t_lpdf_eval(C.byref(a)))
+    res = {"rc": rc, "lp": float(lp[0])}
+    for name, bit, g, o in zip(("dy", "dnu", "dmu", "dsigma"),
+                               (_abi.NEED_DY, _abi.NEED_DNU, _abi.NEED_DALPHA, _abi.NEED_DSIGMA), grads, ops):
+        if flags & bit:
+            res[name] = g[:o.size]
+    return res
+
+
+def student_t_lpdf(y, nu, mu, sigma, propto=False, y_var=False, nu_var=True, mu_var=True, sigma_var=True,
+                   y_is_data=True):
+    """student_t_lpdf(y | nu, mu, sigma), stan/math/prim/scal/prob/student_t_lpdf.hpp:55-201; grads for the operands
+    marked *_var.  Call sequence of the reference: size_zero -> 0 (:57-59), the four domain checks (:67-70), the
+    size check (:71-73), nothing to compute under propto with constant operands -> 0 (:75-77)."""
+    function = "student_t_lpdf"
+    ops = [_f64(v) for v in (y, nu, mu, sigma)]
+    names = ("Random variable", "Degrees of freedom parameter", "Location parameter", "Scale parameter")
+    if min(o.size for o in ops) == 0:
+        return 0.0, {}
+
+    def domain_checks():
+        if np.any(np.isnan(ops[0])):
+            raise DomainError("%s: %s is nan, but must not be nan!" % (function, names[0]))
+        for q in (1, 3):
+            if not np.all((ops[q] > 0) & np.isfinite(ops[q])):
+                raise DomainError("%s: %s must be positive finite!" % (function, names[q]))
+            if q == 1 and not np.all(np.isfinite(ops[2])):
+                raise DomainError("%s: %s must be finite!" % (function, names[2]))
+
+    n = max(o.size for o in ops)
+    sizes_ok = all(o.size in (1, n) for o in ops)
+    var_mask = (1 if y_var else 0) | (2 if nu_var else 0) | (4 if mu_var else 0) | (8 if sigma_var else 0)
+    if not sizes_ok or (propto and var_mask == 0):
+        domain_checks()   # no device work: the reference's eager checks, in its order
+        for name, o in zip(names, ops):
+            if o.size not in (1, n):
+                raise ValueError("%s: %s has dimension = %d, expecting dimension = %d" % (function, name, o.size, n))
+        return 0.0, {}
+    need = ((_abi.NEED_DY if y_var else 0) | (_abi.NEED_DNU if nu_var else 0) | (_abi.NEED_DALPHA if mu_var else 0)
+            | (_abi.NEED_DSIGMA if sigma_var else 0))
+    if propto:
+        lpf = (_abi.LP_DOF if nu_var else 0) | (_abi.LP_SCALE if sigma_var else 0) | _abi.LP_MAIN
+    else:
+        lpf = _abi.LP_CONST | _abi.LP_DOF | _abi.LP_SCALE | _abi.LP_MAIN
+    r = student_t_eval(ops[0], ops[1], ops[2], ops[3], need | lpf, y_is_data=y_is_data and not y_var)
+    if r["rc"] == _abi.BAD_OPERAND:   # the kernel saw a bad element: the reference's checks name it
+        domain_checks()
+        raise DomainError("%s: operand outside the domain" % function)
+    grads = {}
+    for key, name in (("dy", "y"), ("dnu", "nu"), ("dmu", "mu"), ("dsigma", "sigma")):
+        if key in r:
+            grads[name] = r[key]
+    return r["lp"], grads
+
+
 class GlmBatch:
     """`count` independent GLMs of one family and one K evaluated with ONE kernel launch per device
     (stan_cuda_glm_eval_batch): the jobs of a map_rect call whose functor is a single GLM call.

@@ -361,6 +361,58 @@ int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a) {
   return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+/* stan/math/prim/scal/prob/student_t_lpdf.hpp:55-201.  The eager checks (:67-70) become BAD_OPERAND; scalar
+ * operands accumulate their partial over n (prim/scal/meta/broadcast_array.hpp:9-33). */
+#define ORACLE_NEG_LOG_SQRT_PI (-0.5723649429247000870717135)
+int oracle_student_t_lpdf_eval(const stan_cuda_student_t_args* a) {
+  if (!a || a->n < 0) return STAN_CUDA_ERR_ARG;
+  if (a->n == 0) {                                                              /* :57-59 */
+    if (a->lp) *a->lp = 0.0;
+    return STAN_CUDA_OK;
+  }
+  for (int64_t i = 0; i < a->y_len; ++i) if (isnan(a->y[i])) return STAN_CUDA_BAD_OPERAND;                       /* :67 */
+  for (int64_t i = 0; i < a->nu_len; ++i) if (!(a->nu[i] > 0.0) || !isfinite(a->nu[i])) return STAN_CUDA_BAD_OPERAND;   /* :68 */
+  for (int64_t i = 0; i < a->mu_len; ++i) if (!isfinite(a->mu[i])) return STAN_CUDA_BAD_OPERAND;                 /* :69 */
+  for (int64_t i = 0; i < a->sigma_len; ++i)
+    if (!(a->sigma[i] > 0.0) || !isfinite(a->sigma[i])) return STAN_CUDA_BAD_OPERAND;                            /* :70 */
+  const int ym = a->y_len != 1, nm = a->nu_len != 1, mm = a->mu_len != 1, sm = a->sigma_len != 1;
+  const int need_y = (a->flags & STAN_CUDA_NEED_DY) && a->dy;
+  const int need_nu = (a->flags & STAN_CUDA_NEED_DNU) && a->dnu;
+  const int need_mu = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dmu;
+  const int need_sigma = (a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma;
+  if (need_y) for (int64_t i = 0; i < a->y_len; ++i) a->dy[i] = 0.0;
+  if (need_nu) for (int64_t i = 0; i < a->nu_len; ++i) a->dnu[i] = 0.0;
+  if (need_mu) for (int64_t i = 0; i < a->mu_len; ++i) a->dmu[i] = 0.0;
+  if (need_sigma) for (int64_t i = 0; i < a->sigma_len; ++i) a->dsigma[i] = 0.0;
+  double logp = 0.0;
+  for (int64_t n = 0; n < a->n; ++n) {
+    const double y = a->y[ym ? n : 0], nu = a->nu[nm ? n : 0], mu = a->mu[mm ? n : 0], sg = a->sigma[sm ? n : 0];
+    const double half_nu = 0.5 * nu;                                                                 /* :90 */
+    const double zs = (y - mu) / sg;
+    const double sq = zs * zs / nu;                                                                  /* :145-146 */
+    const double l1p = log1p(sq);                                                                    /* :147 */
+    if (a->flags & STAN_CUDA_LP_CONST) logp += ORACLE_NEG_LOG_SQRT_PI;                               /* :158-160 */
+    if (a->flags & STAN_CUDA_LP_DOF) logp += lgamma(half_nu + 0.5) - lgamma(half_nu) - 0.5 * log(nu);  /* :161-163 */
+    if (a->flags & STAN_CUDA_LP_SCALE) logp -= log(sg);                                              /* :164-166 */
+    if (a->flags & STAN_CUDA_LP_MAIN) logp -= (half_nu + 0.5) * l1p;                                 /* :167-169 */
+    if (need_y)                                                                                      /* :171-176 */
+      a->dy[ym ? n : 0] += -(half_nu + 0.5) * 1.0 / (1.0 + sq) * (2.0 * (y - mu) / (sg * sg) / nu);
+    if (need_nu) {                                                                                   /* :177-185 */
+      const double inv_nu = 1.0 / nu;
+      a->dnu[nm ? n : 0] += 0.5 * oracle_digamma(half_nu + 0.5) - 0.5 * oracle_digamma(half_nu) - 0.5 * inv_nu - 0.5 * l1p
+                            + (half_nu + 0.5) * (1.0 / (1.0 + sq) * sq * inv_nu);
+    }
+    if (need_mu)                                                                                     /* :186-191 */
+      a->dmu[mm ? n : 0] -= (half_nu + 0.5) / (1.0 + sq) * (2.0 * (mu - y) / (sg * sg * nu));
+    if (need_sigma) {                                                                                /* :192-198 */
+      const double inv_sigma = 1.0 / sg;
+      a->dsigma[sm ? n : 0] += -inv_sigma + (nu + 1.0) / (1.0 + sq) * (sq * inv_sigma);
+    }
+  }
+  if (a->lp) *a->lp = logp;
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
 /* Vectorised elementwise densities with an integer outcome.
  *   bernoulli_logit_lpmf  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
  *   poisson_log_lpmf      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93

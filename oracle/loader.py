@@ -39,6 +39,8 @@ def oracle_lib():
         lib.oracle_glm_eval.argtypes = [C.POINTER(_abi.GlmArgs)]
         lib.oracle_normal_lpdf_eval.restype = C.c_int
         lib.oracle_normal_lpdf_eval.argtypes = [C.POINTER(_abi.NormalArgs)]
+        lib.oracle_student_t_lpdf_eval.restype = C.c_int
+        lib.oracle_student_t_lpdf_eval.argtypes = [C.POINTER(_abi.StudentTArgs)]
         lib.oracle_density_eval.restype = C.c_int
         lib.oracle_density_eval.argtypes = [C.POINTER(_abi.DensityArgs)]
         _oracle = lib
@@ -73,6 +75,10 @@ def ref_lib():
         if hasattr(lib, "stanref_density"):
             lib.stanref_density.restype = i
             lib.stanref_density.argtypes = [i, i, l, vp, l, dp, l, i, dp, dp, dp, C.c_char_p, i]
+        if hasattr(lib, "stanref_student_t_lpdf"):
+            lib.stanref_student_t_lpdf.restype = i
+            lib.stanref_student_t_lpdf.argtypes = [i, i, dp, l, dp, l, dp, l, dp, l, dp, dp, dp, dp, dp, dp,
+                                                   C.c_char_p, i]
         lib.stanref_init_threads.restype = i
         lib.stanref_init_threads.argtypes = [i]
         lib.stanref_shards_create.restype = C.c_void_p
@@ -341,6 +347,70 @@ def ref_normal_lpdf(y, mu, sigma, propto=False, need_dy=False):
     res = {"rc": 0, "lp": float(lp[0]), "dmu": dmu, "dsigma": dsigma, "seconds": float(secs[0])}
     if need_dy:
         res["dy"] = dy
+    return res
+
+
+# ------------------------------------------------------------------------------------------
+# student_t_lpdf(y | nu, mu, sigma).  var_mask bit 0: y, 1: nu, 2: mu, 3: sigma are autodiff variables.
+def student_t_flags(propto=False, var_mask=0b1110):
+    """The summands the reference keeps (student_t_lpdf.hpp:158-169 under include_summand<propto, ...>) and the
+    partials it builds (:171-198 under !is_constant_all<...>) for this mix of data / variables."""
+    need = ((_abi.NEED_DY if var_mask & 1 else 0) | (_abi.NEED_DNU if var_mask & 2 else 0)
+            | (_abi.NEED_DALPHA if var_mask & 4 else 0) | (_abi.NEED_DSIGMA if var_mask & 8 else 0))
+    if not propto:
+        return need | _abi.LP_CONST | _abi.LP_DOF | _abi.LP_SCALE | _abi.LP_MAIN
+    return need | ((_abi.LP_DOF if var_mask & 2 else 0) | (_abi.LP_SCALE if var_mask & 8 else 0)
+                   | (_abi.LP_MAIN if var_mask else 0))
+
+
+def student_t_args(y, nu, mu, sigma, flags, y_is_data=True):
+    ops = [_f64(v) for v in (y, nu, mu, sigma)]
+    n = max(o.size for o in ops) if min(o.size for o in ops) > 0 else 0
+    out = {"lp": np.zeros(1), "_keep": ops}
+    for name, o in zip(("dy", "dnu", "dmu", "dsigma"), ops):
+        out[name] = np.zeros(max(o.size, 1))
+    a = _abi.StudentTArgs()
+    a.flags, a.y_is_data, a.n = flags, int(y_is_data), n
+    a.y, a.y_len, a.nu, a.nu_len = ops[0].ctypes.data, ops[0].size, ops[1].ctypes.data, ops[1].size
+    a.mu, a.mu_len, a.sigma, a.sigma_len = ops[2].ctypes.data, ops[2].size, ops[3].ctypes.data, ops[3].size
+    a.lp, a.dy, a.dnu, a.dmu, a.dsigma = (out[k].ctypes.data for k in ("lp", "dy", "dnu", "dmu", "dsigma"))
+    return a, out, ops
+
+
+def finish_student_t(rc, out, ops, flags):
+    res = {"rc": rc, "lp": float(out["lp"][0])}
+    for name, bit, o in zip(("dy", "dnu", "dmu", "dsigma"),
+                            (_abi.NEED_DY, _abi.NEED_DNU, _abi.NEED_DALPHA, _abi.NEED_DSIGMA), ops):
+        if flags & bit:
+            res[name] = out[name][:o.size].copy()
+    return res
+
+
+def oracle_student_t_lpdf(y, nu, mu, sigma, propto=False, var_mask=0b1110, flags=None):
+    if flags is None:
+        flags = student_t_flags(propto, var_mask)
+    a, out, ops = student_t_args(y, nu, mu, sigma, flags)
+    rc = oracle_lib().oracle_student_t_lpdf_eval(C.byref(a))
+    return finish_student_t(rc, out, ops, flags)
+
+
+def ref_student_t_lpdf(y, nu, mu, sigma, propto=False, var_mask=0b1110):
+    """The compiled reference itself (oracle/ref_shim_student_t.cpp); raises RefError where it throws."""
+    ops = [_f64(v) for v in (y, nu, mu, sigma)]
+    lp, secs = np.zeros(1), np.zeros(1)
+    grads = [np.zeros(max(o.size, 1)) for o in ops]
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_student_t_lpdf(int(propto), int(var_mask), ops[0].ctypes.data, ops[0].size,
+                                          ops[1].ctypes.data, ops[1].size, ops[2].ctypes.data, ops[2].size,
+                                          ops[3].ctypes.data, ops[3].size, lp.ctypes.data, grads[0].ctypes.data,
+                                          grads[1].ctypes.data, grads[2].ctypes.data, grads[3].ctypes.data,
+                                          secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    res = {"rc": 0, "lp": float(lp[0]), "seconds": float(secs[0])}
+    for bit, name, g, o in zip((1, 2, 4, 8), ("dy", "dnu", "dmu", "dsigma"), grads, ops):
+        if var_mask & bit:
+            res[name] = g[:o.size]
     return res
 
 

@@ -16,6 +16,7 @@
 #include <stan/math/cuda/ordered_logistic_glm_lpmf.hpp>
 #include <stan/math/cuda/categorical_logit_glm_lpmf.hpp>
 #include <stan/math/cuda/normal_lpdf.hpp>
+#include <stan/math/cuda/student_t_lpdf.hpp>
 #include <stan/math/cuda/map_rect_devices.hpp>
 #endif
 #endif

@@ -58,6 +58,13 @@ static_assert(cu::normal_lpdf_eligible<std::vector<double>, double, std::vector<
 static_assert(cu::normal_lpdf_eligible<vector_v, vector_v, vector_v>::value, "all var vectors");
 static_assert(!cu::normal_lpdf_eligible<double, var, var>::value, "scalar call stays on the reference loop");
 static_assert(!cu::normal_lpdf_eligible<vector_d, vector_fd, double>::value, "fvar");
+// vectorised student_t_lpdf: at least one container operand (student_t_lpdf.hpp:52-55)
+static_assert(cu::student_t_lpdf_eligible<vector_d, var, vector_v, var>::value, "the model statement");
+static_assert(cu::student_t_lpdf_eligible<std::vector<double>, std::vector<var>, double, std::vector<var>>::value, "vector nu, sigma");
+static_assert(cu::student_t_lpdf_eligible<vector_v, vector_v, vector_v, vector_v>::value, "all var vectors");
+static_assert(cu::student_t_lpdf_eligible<double, double, vector_d, double>::value, "all data");
+static_assert(!cu::student_t_lpdf_eligible<double, var, var, var>::value, "scalar call stays on the reference loops");
+static_assert(!cu::student_t_lpdf_eligible<vector_d, vector_fd, double, double>::value, "fvar");
 // vectorised bernoulli_logit_lpmf / poisson_log_lpmf: container operand of double / var
 static_assert(cu::int_density_eligible<ints, vector_v>::value, "d1 signature");
 static_assert(cu::int_density_eligible<int, std::vector<var>>::value, "scalar n");

@@ -13,6 +13,13 @@ def pytest_configure(config):
 
 
 @pytest.fixture(scope="session")
+def golden_st():
+    """student_t_lpdf vectors from the compiled reference (tests/golden/make_student_t_golden.py)."""
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "student_t_golden.npz"), allow_pickle=False)
+
+
+@pytest.fixture(scope="session")
 def golden():
     import numpy as np
     path = os.path.join(ROOT, "tests", "golden", "glm_golden.npz")

@@ -47,6 +47,46 @@ def normal_case(golden, name):
     return c
 
 
+def student_t_case(golden_st, name):
+    p = "st/%s/" % name
+    c = {k: golden_st[p + k] for k in ("y", "nu", "mu", "sigma")}
+    c["propto"], c["var_mask"], c["lp"] = bool(golden_st[p + "propto"]), int(golden_st[p + "var_mask"]), float(golden_st[p + "lp"])
+    for k in ("dy", "dnu", "dmu", "dsigma"):
+        if p + k in golden_st.files:
+            c[k] = golden_st[p + k]
+    if p + "known_answer" in golden_st.files:
+        c["known_answer"] = float(golden_st[p + "known_answer"])
+    return c
+
+
+def check_student_t_result(r, c, what, rtol=RTOL):
+    """d/dy, d/dmu, d/dsigma: the north-star gate; lp: the same plus the lgamma floor below.  d/dnu (student_t_lpdf.hpp:177-182) is the sum of
+    0.5 * digamma(nu/2 + 1/2) - 0.5 * digamma(nu/2) - 0.5 / nu (terms of size |digamma(nu/2)| that cancel to O(1/nu^2))
+    and the data terms: every implementation -- the reference's boost::math::digamma included -- carries an ABSOLUTE
+    error of a few ulp of digamma(nu/2) per element there, which no relative gate on the cancelled result can hold.
+    The gate for d/dnu is therefore |got - ref| <= rtol * scale + 32 ulp(max(1, |digamma(nu/2)|)) per element summed."""
+    n = max(np.size(c[k]) for k in ("y", "nu", "mu", "sigma"))
+    nu_all = np.broadcast_to(np.asarray(c["nu"], float), (n,)) if np.size(c["nu"]) in (1, n) else np.asarray(c["nu"], float)
+    # lp holds lgamma(nu/2 + 1/2) - lgamma(nu/2) per element (:161-163): two numbers of size |lgamma(nu/2)| whose
+    # difference is O(log nu) -- any two lgamma implementations (glibc's on the host, CUDA's on the device) differ by
+    # a few ulp OF lgamma(nu/2) there.  Invisible for nu < 100, 1e-7 per element at nu = 1e8.
+    lgamma_size = np.maximum(1.0, nu_all / 2 * np.maximum(np.log(nu_all / 2), 1.0))
+    lp_floor = float(np.sum(8 * np.finfo(float).eps * lgamma_size))
+    assert abs(r["lp"] - c["lp"]) <= rtol * abs(c["lp"]) + lp_floor, "%s lp: got %r ref %r" % (what, r["lp"], c["lp"])
+    for k in ("dy", "dmu", "dsigma"):
+        if k in c:
+            assert_close(r[k], c[k], what + " " + k, rtol)
+    if "dnu" in c:
+        got, ref = np.asarray(r["dnu"], float), np.asarray(c["dnu"], float)
+        assert got.shape == ref.shape
+        nu = np.asarray(c["nu"], float)
+        digamma_size = np.maximum(1.0, np.maximum(np.abs(np.log(nu / 2)), 2.0 / nu))   # |digamma(x)| ~ max(|log x|, 1/x)
+        floor = 32 * np.finfo(float).eps * digamma_size * (n if nu.size == 1 else 1)
+        scale = np.maximum(np.abs(ref), 1e-6 * np.max(np.abs(ref)))
+        excess = np.abs(got - ref) - (rtol * scale + floor)
+        assert np.all(excess <= 0), "%s dnu: |got - ref| exceeds rtol * scale + digamma ulp floor by %.3e" % (what, float(np.max(excess)))
+
+
 def check_glm_result(r, c, what, rtol=RTOL):
     assert_close(r["lp"], c["lp"], what + " lp", rtol)
     assert_close(r["dbeta"], c["dbeta"], what + " dbeta", rtol)

@@ -25,6 +25,7 @@
 
 int oracle_glm_eval(const stan_cuda_glm_args* a);
 int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a);
+int oracle_student_t_lpdf_eval(const stan_cuda_student_t_args* a);
 int oracle_density_eval(const stan_cuda_density_args* a);
 
 static __thread char tl_error[256];
@@ -154,6 +155,13 @@ int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) {
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
   TIMED(oracle_normal_lpdf_eval(a));
   return rc < 0 ? fail(rc, "stan_cuda_normal_lpdf_eval: bad argument") : rc;
+}
+
+int stan_cuda_student_t_lpdf_eval(const stan_cuda_student_t_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_student_t_lpdf_eval: null args");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  TIMED(oracle_student_t_lpdf_eval(a)); /* code 3 for the operands student_t_lpdf.hpp:67-70 rejects */
+  return rc < 0 ? fail(rc, "stan_cuda_student_t_lpdf_eval: bad argument") : rc;
 }
 
 int stan_cuda_density_eval(const stan_cuda_density_args* a) {

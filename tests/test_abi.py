@@ -38,6 +38,7 @@ def test_struct_layout_matches_header(cdll):
     # sizes implied by the header's field order on LP64
     assert ctypes.sizeof(_abi.GlmArgs) == 4 + 4 + 8 + 8 + 8 + 8 + 4 + 4 + 8 * 16 + 4 + 4 + 8 + 8
     assert ctypes.sizeof(_abi.NormalArgs) == 4 + 4 + 8 * 11
+    assert ctypes.sizeof(_abi.StudentTArgs) == 4 + 4 + 8 * 14
     assert ctypes.sizeof(_abi.Stats) == 8 * 9
 
 
