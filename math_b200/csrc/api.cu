@@ -965,6 +965,7 @@ int student_t_lpdf_eval(const stan_cuda_student_t_args* a) {
   io.n = n;
   io.result = p; p += 8;
   io.y0 = a->y[0]; io.nu0 = a->nu[0]; io.mu0 = a->mu[0]; io.sigma0 = a->sigma[0];
+  if (!vec[1]) student_t_scalar_dof_terms(&io);  // io.nu stays null for a scalar nu
   const double** in_slot[4] = {&io.y, &io.nu, &io.mu, &io.sigma};
   double** out_slot[4] = {&io.dy_row, &io.dnu_row, &io.dmu_row, &io.dsigma_row};
   for (int q = 0; q < 4; ++q) {

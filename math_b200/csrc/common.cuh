@@ -204,9 +204,13 @@ struct StudentTIO {
   int64_t n;
   const double* y; const double* nu; const double* mu; const double* sigma;  // device vectors, or null for a scalar operand
   double y0, nu0, mu0, sigma0;                                              // scalar operands by value
+  // scalar nu: the per-nu terms of :94-117, evaluated once on the host (student_t_scalar_dof_terms)
+  double dof_term0;   // lgamma(nu/2 + 1/2) - lgamma(nu/2) - log(nu)/2
+  double dnu_const0;  // digamma(nu/2 + 1/2)/2 - digamma(nu/2)/2 - 1/(2 nu)
   double* dy_row; double* dnu_row; double* dmu_row; double* dsigma_row;     // per-element outputs (vector operands) or null
   double* result;  // [8]: lp, sum dy, sum dnu, sum dmu, sum dsigma, witness, bad-operand bits, 0
 };
+void student_t_scalar_dof_terms(StudentTIO* io);
 int launch_student_t_lpdf(const StudentTIO& io, Workspace* ws, int device, cudaStream_t stream);
 
 // vectorised elementwise densities (density.cu)

@@ -89,20 +89,27 @@ __global__ void __launch_bounds__(THREADS) density_kernel(const DensityKernelPar
   __syncthreads();
   if (!s_is_last) return;
   __threadfence();
-  if (threadIdx.x < 2) {
+  // warp q sums column q of the per-CTA partials: lane l takes CTAs l, l + 32, ... in order, then a shuffle tree
+  // (a fixed order: bit-reproducible from call to call); warp 2 ORs the status bits
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  if (warp < 2u) {
     double s = 0.0;
-    for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.scratch + size_t(b) * 4 + threadIdx.x);
-    if (threadIdx.x == 0 && DENSITY == STAN_CUDA_DENSITY_POISSON_LOG && lp_const && io.lgamma_cached) s -= io.lgamma_total;
-    io.result[threadIdx.x] = s;
-    if (threadIdx.x == 0) {
-      io.result[2] = 0.0;
-      io.result[3] = s;  // witness = logp
+    for (unsigned b = lane; b < gridDim.x; b += 32u) s += __ldcg(p.scratch + size_t(b) * 4 + warp);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    if (lane == 0) {
+      if (warp == 0 && DENSITY == STAN_CUDA_DENSITY_POISSON_LOG && lp_const && io.lgamma_cached) s -= io.lgamma_total;
+      io.result[warp] = s;
+      if (warp == 0) {
+        io.result[2] = 0.0;
+        io.result[3] = s;  // witness = logp
+      }
     }
-  }
-  if (threadIdx.x == 2) {
+  } else if (warp == 2u) {
     unsigned all = 0;
-    for (unsigned b = 0; b < gridDim.x; ++b) all |= unsigned(__ldcg(p.scratch + size_t(b) * 4 + 2));
-    io.result[4] = double(all);
+    for (unsigned b = lane; b < gridDim.x; b += 32u) all |= unsigned(__ldcg(p.scratch + size_t(b) * 4 + 2));
+    all = __reduce_or_sync(0xffffffffu, all);
+    if (lane == 0) io.result[4] = double(all);
   }
   __syncthreads();
   if (threadIdx.x == 0) *p.ticket = 0u;

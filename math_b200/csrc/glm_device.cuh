@@ -276,7 +276,7 @@ struct RowTerms {
 // digamma for x > 0: recurrence up to x >= 10, then the asymptotic series
 // ln x - 1/(2x) - sum B_2k / (2k x^2k) with 7 terms (error < 1e-17 at x = 10).  The reference calls
 // boost::math::digamma (stan/math/prim/scal/fun/digamma.hpp); agreement is pinned in the tests.
-__device__ __forceinline__ double digamma_pos(double x) {
+__host__ __device__ __forceinline__ double digamma_pos(double x) {
   double r = 0.0;
   while (x < 10.0) {
     r -= 1.0 / x;

@@ -83,16 +83,24 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
   __syncthreads();
   if (!s_is_last) return;
   __threadfence();
-  if (threadIdx.x < 3) {
+  // warp q sums column q of the per-CTA partials: lane l takes CTAs l, l + 32, ... in order, then a shuffle tree
+  // (a fixed order: bit-reproducible from call to call); warp 3 ORs the bad-operand bits.  A single thread walking
+  // all 1184 partials cost more than the map itself at N = 1e6.
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  if (warp < 3u) {
     double s = 0.0;
-    for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.scratch + size_t(b) * 4 + threadIdx.x);
-    io.result[threadIdx.x] = s;
-    if (threadIdx.x == 0) io.result[3] = s;  // finiteness witness = logp
-  }
-  if (threadIdx.x == 3) {
+    for (unsigned b = lane; b < gridDim.x; b += 32u) s += __ldcg(p.scratch + size_t(b) * 4 + warp);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    if (lane == 0) {
+      io.result[warp] = s;
+      if (warp == 0) io.result[3] = s;  // finiteness witness = logp
+    }
+  } else if (warp == 3u) {
     unsigned all_bad = 0;
-    for (unsigned b = 0; b < gridDim.x; ++b) all_bad |= unsigned(__ldcg(p.scratch + size_t(b) * 4 + 3));
-    io.result[4] = double(all_bad);
+    for (unsigned b = lane; b < gridDim.x; b += 32u) all_bad |= unsigned(__ldcg(p.scratch + size_t(b) * 4 + 3));
+    all_bad = __reduce_or_sync(0xffffffffu, all_bad);
+    if (lane == 0) io.result[4] = double(all_bad);
   }
   __syncthreads();
   if (threadIdx.x == 0) *p.ticket = 0u;

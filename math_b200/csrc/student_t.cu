@@ -5,10 +5,13 @@
 // broadcast_array, prim/scal/meta/broadcast_array.hpp:9-33).
 //
 // The reference precomputes lgamma / digamma of nu/2 and nu/2 + 1/2 once per element of nu (:94-112): for a scalar
-// nu that is once per call, and so it is here (each thread computes them before its loop); for a vector nu they are
-// per-element work in both.  HBM-side this is 8 bytes per vector operand in and 8 per vector partial out; with a
-// vector nu the lgamma / digamma pairs make it FP64-issue-bound instead.
+// nu that is once per call, and so it is here (on the host, student_t_scalar_dof_terms, with the same libm lgamma
+// the reference calls); for a vector nu they are per-element work in both.  HBM-side this is 8 bytes per vector
+// operand in and 8 per vector partial out, but the kernel is bound by FP64 issue (B200: ~40 TFLOP/s), not by HBM:
+// log1p and the divisions for a scalar nu, the lgamma / digamma pairs on top for a vector nu.
 #include <math.h>
+
+#include <cmath>
 
 #include "glm_device.cuh"
 
@@ -22,7 +25,7 @@ struct StudentTKernelParams {
 
 constexpr int kStSums = 5;  // lp, dy, dnu, dmu, dsigma
 
-template <int THREADS>
+template <int THREADS>  // at least (kStSums + 1) warps
 __global__ void __launch_bounds__(THREADS) student_t_lpdf_kernel(const StudentTKernelParams p) {
   const StudentTIO& io = p.io;
   const double NEG_LOG_SQRT_PI = -0.5723649429247000870717135;  // prim/scal/fun/constants.hpp:162
@@ -34,52 +37,53 @@ __global__ void __launch_bounds__(THREADS) student_t_lpdf_kernel(const StudentTK
   double acc[kStSums] = {0.0, 0.0, 0.0, 0.0, 0.0};
   // domain of the operands, checked here instead of in four O(N) host loops (:67-70)
   unsigned bad = 0;  // bit 0: y NaN, 1: nu not positive finite, 2: mu not finite, 3: sigma not positive finite
-  // per-nu terms, hoisted for a scalar nu
-  double dof_term = 0.0, dnu_const = 0.0, log_sigma0 = 0.0;
-  if (!io.nu) {
-    const double h = 0.5 * io.nu0;
-    if (lp_dof) dof_term = lgamma(h + 0.5) - lgamma(h) - 0.5 * log(io.nu0);                              // :98-99, :117, :158-160
-    if (want_nu && io.nu0 > 0.0) dnu_const = 0.5 * digamma_pos(h + 0.5) - 0.5 * digamma_pos(h) - 0.5 * (1.0 / io.nu0);  // :108-109, :177-180
-  }
-  if (!io.sigma && lp_scale) log_sigma0 = log(io.sigma0);                                                // :125
+  // The loop is FP64-issue-bound, not HBM-bound (a division is ~20 issue slots, log1p ~50): everything that
+  // depends only on a scalar operand is hoisted, and the quotients of :145-146, :171-173, :186-188 are written
+  // with the two reciprocals 1/sigma and 1/nu (one division each, none for a scalar) and ONE more division,
+  // 1/(1 + sq).  d/dy and d/dmu share their factor: the reference's two expressions differ in rounding only.
+  const bool nu_vec = io.nu != nullptr, sigma_vec = io.sigma != nullptr;
+  const double inv_sigma0 = 1.0 / io.sigma0, inv_nu0 = 1.0 / io.nu0;
+  const double log_sigma0 = lp_scale && !sigma_vec ? log(io.sigma0) : 0.0;                               // :125
   for (int64_t i = blockIdx.x * int64_t(THREADS) + threadIdx.x; i < io.n; i += int64_t(gridDim.x) * THREADS) {
     const double y = io.y ? io.y[i] : io.y0;
-    const double nu = io.nu ? io.nu[i] : io.nu0;
+    const double nu = nu_vec ? io.nu[i] : io.nu0;
     const double mu = io.mu ? io.mu[i] : io.mu0;
-    const double sg = io.sigma ? io.sigma[i] : io.sigma0;
+    const double sg = sigma_vec ? io.sigma[i] : io.sigma0;
     bad |= (isnan(y) ? 1u : 0u) | ((nu > 0.0 && isfinite(nu)) ? 0u : 2u) | (isfinite(mu) ? 0u : 4u) |
            ((sg > 0.0 && isfinite(sg)) ? 0u : 8u);
-    const double half_nu = 0.5 * nu;                                                                     // :90
-    const double zs = (y - mu) / sg;
-    const double sq = zs * zs / nu;                                                                      // :145-146
+    const double inv_sigma = sigma_vec ? 1.0 / sg : inv_sigma0;
+    const double inv_nu = nu_vec ? 1.0 / nu : inv_nu0;
+    const double hp = 0.5 * nu + 0.5;                                                                    // :90, half_nu + 0.5
+    const double diff = y - mu;
+    const double zs = diff * inv_sigma;
+    const double sq = zs * zs * inv_nu;                                                                  // :145-146
     const double l1p = log1p(sq);                                                                        // :147
     const double inv_1p = 1.0 / (1.0 + sq);
     double lp = 0.0;
     if (lp_const) lp += NEG_LOG_SQRT_PI;                                                                 // :155-157
-    if (lp_dof) lp += io.nu ? lgamma(half_nu + 0.5) - lgamma(half_nu) - 0.5 * log(nu) : dof_term;        // :158-160
-    if (lp_scale) lp -= io.sigma ? log(sg) : log_sigma0;                                                 // :161-163
-    if (lp_main) lp -= (half_nu + 0.5) * l1p;                                                            // :164-166
+    if (lp_dof) lp += nu_vec ? lgamma(hp) - lgamma(0.5 * nu) - 0.5 * log(nu) : io.dof_term0;             // :158-160
+    if (lp_scale) lp -= sigma_vec ? log(sg) : log_sigma0;                                                // :161-163
+    if (lp_main) lp -= hp * l1p;                                                                         // :164-166
     acc[0] += lp;
-    if (want_y) {                                                                                        // :168-173
-      const double d = -(half_nu + 0.5) * 1.0 * inv_1p * (2.0 * (y - mu) / (sg * sg) / nu);
-      acc[1] += d;
-      if (io.dy_row) io.dy_row[i] = d;
+    if (want_y || want_mu) {                                                                             // :168-173, :183-188
+      const double d = hp * inv_1p * (2.0 * diff * (inv_sigma * inv_sigma) * inv_nu);                    // = d/dmu = -d/dy
+      if (want_y) {
+        acc[1] -= d;
+        if (io.dy_row) io.dy_row[i] = -d;
+      }
+      if (want_mu) {
+        acc[3] += d;
+        if (io.dmu_row) io.dmu_row[i] = d;
+      }
     }
     if (want_nu) {                                                                                       // :174-182
-      const double inv_nu = 1.0 / nu;
-      double c = dnu_const;
-      if (io.nu) c = nu > 0.0 ? 0.5 * digamma_pos(half_nu + 0.5) - 0.5 * digamma_pos(half_nu) - 0.5 * inv_nu : 0.0;
-      const double d = c - 0.5 * l1p + (half_nu + 0.5) * (inv_1p * sq * inv_nu);
+      double c = io.dnu_const0;
+      if (nu_vec) c = nu > 0.0 ? 0.5 * digamma_pos(hp) - 0.5 * digamma_pos(0.5 * nu) - 0.5 * inv_nu : 0.0;
+      const double d = c - 0.5 * l1p + hp * (inv_1p * sq * inv_nu);
       acc[2] += d;
       if (io.dnu_row) io.dnu_row[i] = d;
     }
-    if (want_mu) {                                                                                       // :183-188
-      const double d = -((half_nu + 0.5) * inv_1p * (2.0 * (mu - y) / (sg * sg * nu)));
-      acc[3] += d;
-      if (io.dmu_row) io.dmu_row[i] = d;
-    }
     if (want_sigma) {                                                                                    // :189-196
-      const double inv_sigma = 1.0 / sg;
       const double d = -inv_sigma + (nu + 1.0) * inv_1p * (sq * inv_sigma);
       acc[4] += d;
       if (io.dsigma_row) io.dsigma_row[i] = d;
@@ -116,20 +120,40 @@ __global__ void __launch_bounds__(THREADS) student_t_lpdf_kernel(const StudentTK
   __syncthreads();
   if (!s_is_last) return;
   __threadfence();
-  if (threadIdx.x < kStSums) {
+  // warp q sums column q of the per-CTA partials: lane l takes CTAs l, l + 32, ... in order, then a shuffle tree
+  // (a fixed order: the result is bit-reproducible from call to call); warp kStSums ORs the bad-operand bits
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  if (warp < unsigned(kStSums)) {
     double s = 0.0;
-    for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.scratch + size_t(b) * 8 + threadIdx.x);
-    io.result[threadIdx.x] = s;
-    if (threadIdx.x == 0) io.result[5] = s;  // finiteness witness = logp
-  }
-  if (threadIdx.x == kStSums) {
+    for (unsigned b = lane; b < gridDim.x; b += 32u) s += __ldcg(p.scratch + size_t(b) * 8 + warp);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    if (lane == 0) {
+      io.result[warp] = s;
+      if (warp == 0) io.result[5] = s;  // finiteness witness = logp
+    }
+  } else if (warp == unsigned(kStSums)) {
     unsigned all_bad = 0;
-    for (unsigned b = 0; b < gridDim.x; ++b) all_bad |= unsigned(__ldcg(p.scratch + size_t(b) * 8 + kStSums));
-    io.result[6] = double(all_bad);
-    io.result[7] = 0.0;
+    for (unsigned b = lane; b < gridDim.x; b += 32u) all_bad |= unsigned(__ldcg(p.scratch + size_t(b) * 8 + kStSums));
+    all_bad = __reduce_or_sync(0xffffffffu, all_bad);
+    if (lane == 0) {
+      io.result[6] = double(all_bad);
+      io.result[7] = 0.0;
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) *p.ticket = 0u;
+}
+
+void student_t_scalar_dof_terms(StudentTIO* io) {
+  io->dof_term0 = 0.0;
+  io->dnu_const0 = 0.0;
+  const double nu = io->nu0;
+  if (io->nu || !(nu > 0.0) || !std::isfinite(nu)) return;  // vector nu: per element in the kernel; bad nu: the kernel reports it
+  const double h = 0.5 * nu;
+  int sign = 0;  // lgamma_r: no write to the global signgam (the reference's lgamma under STAN_THREADS, prim/scal/fun/lgamma.hpp)
+  io->dof_term0 = ::lgamma_r(h + 0.5, &sign) - ::lgamma_r(h, &sign) - 0.5 * std::log(nu);                              // :98-99, :117, :158-160
+  io->dnu_const0 = 0.5 * digamma_pos(h + 0.5) - 0.5 * digamma_pos(h) - 0.5 * (1.0 / nu);             // :108-109, :177-180
 }
 
 int launch_student_t_lpdf(const StudentTIO& io, Workspace* ws, int device, cudaStream_t stream) {
