@@ -228,6 +228,33 @@ typedef struct stan_cuda_student_t_args {
   double* dsigma;      /* [sigma_len] */
 } stan_cuda_student_t_args;
 
+/* ---- dense FP64 matrices on the device and their product ------------------------------
+ * What the reference's OpenCL backend provides to its `multiply` hooks (stan/math/prim/mat/fun/multiply.hpp:71-79,
+ * stan/math/rev/mat/fun/multiply.hpp:88-99, 111-123, 274-303, 444-473):
+ *   stan_cuda_matrix            matrix_cl<double>            stan/math/opencl/matrix_cl.hpp:32-454
+ *   stan_cuda_matrix_upload     to_matrix_cl / matrix_cl(A)  stan/math/opencl/copy.hpp:37-58
+ *   stan_cuda_matrix_download   from_matrix_cl               stan/math/opencl/copy.hpp:69-93
+ *   stan_cuda_matrix_multiply   A * B, transpose(A) * B ...  stan/math/opencl/multiply.hpp, transpose.hpp
+ * Column-major like Eigen.  Every call returns with nothing in flight, so a handle may be used from any host
+ * thread afterwards (not from two threads at once).  A matrix lives on the device of the calling thread's shard
+ * scope (stan_cuda_shard_scope_enter), else on the first device. */
+typedef struct stan_cuda_matrix stan_cuda_matrix;
+
+/* C (m x n) = op(A) * op(B) with host matrices: upload, product, download in one call (the prim hook and each
+ * product of the rev hook when nothing stays resident).  op(A) is m x k, op(B) is k x n; trans_* != 0 means the
+ * host array holds the transpose (k x m resp. n x k, column-major). */
+typedef struct stan_cuda_multiply_args {
+  int64_t m, n, k;
+  const double* a;
+  int64_t lda;
+  int32_t trans_a;
+  int32_t trans_b;
+  const double* b;
+  int64_t ldb;
+  double* c;
+  int64_t ldc;
+} stan_cuda_multiply_args;
+
 typedef struct stan_cuda_stats_t {
   uint64_t cache_hits;
   uint64_t cache_misses;
@@ -289,6 +316,17 @@ STAN_CUDA_API int stan_cuda_density_eval(const stan_cuda_density_args* a);
  * (student_t_lpdf.hpp:67-70; tested per element inside the kernel, the wrapper then runs the reference's own
  * checks to throw the identical exception). */
 STAN_CUDA_API int stan_cuda_student_t_lpdf_eval(const stan_cuda_student_t_args* a);
+/* dense matrices (see stan_cuda_matrix above).  create: rows x cols of zeros. */
+STAN_CUDA_API int stan_cuda_matrix_create(int64_t rows, int64_t cols, stan_cuda_matrix** out);
+STAN_CUDA_API void stan_cuda_matrix_free(stan_cuda_matrix* m);
+STAN_CUDA_API int64_t stan_cuda_matrix_rows(const stan_cuda_matrix* m);
+STAN_CUDA_API int64_t stan_cuda_matrix_cols(const stan_cuda_matrix* m);
+STAN_CUDA_API int stan_cuda_matrix_upload(stan_cuda_matrix* m, const double* host, int64_t ld);
+STAN_CUDA_API int stan_cuda_matrix_download(const stan_cuda_matrix* m, double* host, int64_t ld);
+/* c = op(a) * op(b); c must have been created with the shape of the product and must not be an operand */
+STAN_CUDA_API int stan_cuda_matrix_multiply(const stan_cuda_matrix* a, int trans_a, const stan_cuda_matrix* b, int trans_b,
+                                            stan_cuda_matrix* c);
+STAN_CUDA_API int stan_cuda_multiply(const stan_cuda_multiply_args* a);
 /* Page-locked staging memory of the calling thread (at least `bytes`, valid until the thread's next
  * call with a larger size).  Operands gathered into it upload by DMA without a bounce buffer. */
 STAN_CUDA_API void* stan_cuda_host_staging(size_t bytes);

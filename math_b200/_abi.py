@@ -100,6 +100,22 @@ class StudentTArgs(C.Structure):
     ]
 
 
+class MultiplyArgs(C.Structure):
+    _fields_ = [
+        ("m", C.c_int64),
+        ("n", C.c_int64),
+        ("k", C.c_int64),
+        ("a", C.c_void_p),
+        ("lda", C.c_int64),
+        ("trans_a", C.c_int32),
+        ("trans_b", C.c_int32),
+        ("b", C.c_void_p),
+        ("ldb", C.c_int64),
+        ("c", C.c_void_p),
+        ("ldc", C.c_int64),
+    ]
+
+
 DENSITY_BERNOULLI_LOGIT, DENSITY_POISSON_LOG = 1, 2
 DENSITIES = {"bernoulli_logit": DENSITY_BERNOULLI_LOGIT, "poisson_log": DENSITY_POISSON_LOG}
 
@@ -150,6 +166,14 @@ PROTOTYPES = {
     "stan_cuda_density_eval": (C.c_int, [C.POINTER(DensityArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
     "stan_cuda_student_t_lpdf_eval": (C.c_int, [C.POINTER(StudentTArgs)]),
+    "stan_cuda_matrix_create": (C.c_int, [C.c_int64, C.c_int64, C.POINTER(C.c_void_p)]),
+    "stan_cuda_matrix_free": (None, [C.c_void_p]),
+    "stan_cuda_matrix_rows": (C.c_int64, [C.c_void_p]),
+    "stan_cuda_matrix_cols": (C.c_int64, [C.c_void_p]),
+    "stan_cuda_matrix_upload": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
+    "stan_cuda_matrix_download": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
+    "stan_cuda_matrix_multiply": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    "stan_cuda_multiply": (C.c_int, [C.POINTER(MultiplyArgs)]),
     "stan_cuda_host_staging": (C.c_void_p, [C.c_size_t]),
     "stan_cuda_cache_invalidate": (C.c_int, [C.c_void_p]),
     "stan_cuda_cache_clear": (None, []),

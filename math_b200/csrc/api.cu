@@ -918,6 +918,12 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+// device of the calling thread's shard scope, else the first device (gemm.cu)
+int scope_device_ordinal() {
+  Context& c = context();
+  return tl_scope.active ? c.devices[size_t(tl_scope.device) % c.devices.size()] : c.devices[0];
+}
+
 // student_t_lpdf (student_t.cu): the four operands travel like those of normal_lpdf -- a length-n data y is cached
 // on the device, every other vector is uploaded per call, scalars go by value
 int student_t_lpdf_eval(const stan_cuda_student_t_args* a) {

@@ -1,0 +1,90 @@
+"""Dense FP64 matrices on the device and their product: the ctypes mirror of what the reference's
+OpenCL backend gives its `multiply` hooks -- matrix_cl (stan/math/opencl/matrix_cl.hpp:32-454), to_matrix_cl /
+from_matrix_cl (opencl/copy.hpp:37-93), transpose and operator* (opencl/multiply.hpp) -- used by the tests and the
+benchmark.  Column-major like Eigen; numpy arrays are converted with order="F"."""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from ._lib import check, lib
+
+
+def _fmat(a):
+    a = np.asarray(a, dtype=np.float64)
+    if a.ndim != 2:
+        raise ValueError("expected a matrix")
+    return np.asfortranarray(a)
+
+
+class MatrixCuda:
+    """matrix_cl<double>: a rows x cols matrix in device memory.  `MatrixCuda(A)` uploads (to_matrix_cl),
+    `.to_host()` downloads (from_matrix_cl), `a @ b` / `multiply(a, b)` is the product, `.T` a transposed view."""
+
+    def __init__(self, a=None, rows=None, cols=None):
+        self._h = C.c_void_p()
+        self._trans = False
+        self._owner = None
+        if a is not None:
+            a = _fmat(a)
+            rows, cols = a.shape
+        check(lib().stan_cuda_matrix_create(int(rows), int(cols), C.byref(self._h)))
+        if a is not None and a.size:
+            check(lib().stan_cuda_matrix_upload(self._h, a.ctypes.data, max(a.shape[0], 1)))
+
+    @property
+    def shape(self):
+        r, c = lib().stan_cuda_matrix_rows(self._h), lib().stan_cuda_matrix_cols(self._h)
+        return (c, r) if self._trans else (r, c)
+
+    @property
+    def T(self):
+        v = MatrixCuda.__new__(MatrixCuda)
+        v._h, v._trans, v._owner = self._h, not self._trans, self._owner or self
+        return v
+
+    def to_host(self):
+        r, c = lib().stan_cuda_matrix_rows(self._h), lib().stan_cuda_matrix_cols(self._h)
+        out = np.zeros((r, c), order="F")
+        if out.size:
+            check(lib().stan_cuda_matrix_download(self._h, out.ctypes.data, max(r, 1)))
+        return out.T if self._trans else out
+
+    def __matmul__(self, other):
+        return multiply(self, other)
+
+    def __del__(self):
+        if getattr(self, "_owner", None) is None and getattr(self, "_h", None):
+            try:
+                lib().stan_cuda_matrix_free(self._h)
+            except Exception:
+                pass
+            self._h = None
+
+
+def multiply(a, b):
+    """Product of two MatrixCuda (views): a new MatrixCuda.  Raises ValueError where the reference's
+    check_multiplicable throws std::invalid_argument (prim/mat/fun/multiply.hpp:69)."""
+    (m, ka), (kb, n) = a.shape, b.shape
+    if ka != kb:
+        raise ValueError("multiply: Columns of m1 (%d) and Rows of m2 (%d) must match in size" % (ka, kb))
+    c = MatrixCuda(rows=m, cols=n)
+    check(lib().stan_cuda_matrix_multiply(a._h, int(a._trans), b._h, int(b._trans), c._h))
+    return c
+
+
+def multiply_host(a, b, trans_a=False, trans_b=False):
+    """op(a) @ op(b) for host matrices through stan_cuda_multiply (upload, product, download in one call)."""
+    a, b = _fmat(a), _fmat(b)
+    m, ka = (a.shape[1], a.shape[0]) if trans_a else a.shape
+    kb, n = (b.shape[1], b.shape[0]) if trans_b else b.shape
+    if ka != kb:
+        raise ValueError("multiply: Columns of m1 (%d) and Rows of m2 (%d) must match in size" % (ka, kb))
+    c = np.zeros((m, n), order="F")
+    g = _abi.MultiplyArgs()
+    g.m, g.n, g.k = m, n, ka
+    g.a, g.lda, g.trans_a = a.ctypes.data, max(a.shape[0], 1), int(trans_a)
+    g.b, g.ldb, g.trans_b = b.ctypes.data, max(b.shape[0], 1), int(trans_b)
+    g.c, g.ldc = c.ctypes.data, max(m, 1)
+    check(lib().stan_cuda_multiply(C.byref(g)))
+    return c

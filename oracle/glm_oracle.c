@@ -413,6 +413,24 @@ int oracle_student_t_lpdf_eval(const stan_cuda_student_t_args* a) {
   return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+/* Dense product C = op(A) * op(B): what Eigen computes for the reference's `multiply`
+ * (stan/math/prim/mat/fun/multiply.hpp:66-83) and for the three products of multiply_mat_vari
+ * (stan/math/rev/mat/fun/multiply.hpp:99, 128-131), as the textbook triple loop with k ascending. */
+int oracle_multiply(const stan_cuda_multiply_args* g) {
+  if (!g || g->m < 0 || g->n < 0 || g->k < 0) return STAN_CUDA_ERR_ARG;
+  for (int64_t j = 0; j < g->n; ++j)
+    for (int64_t i = 0; i < g->m; ++i) {
+      double s = 0.0;
+      for (int64_t l = 0; l < g->k; ++l) {
+        const double av = g->trans_a ? g->a[i * g->lda + l] : g->a[l * g->lda + i];
+        const double bv = g->trans_b ? g->b[l * g->ldb + j] : g->b[j * g->ldb + l];
+        s += av * bv;
+      }
+      g->c[j * g->ldc + i] = s;
+    }
+  return STAN_CUDA_OK;
+}
+
 /* Vectorised elementwise densities with an integer outcome.
  *   bernoulli_logit_lpmf  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
  *   poisson_log_lpmf      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93

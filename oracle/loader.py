@@ -41,6 +41,8 @@ def oracle_lib():
         lib.oracle_normal_lpdf_eval.argtypes = [C.POINTER(_abi.NormalArgs)]
         lib.oracle_student_t_lpdf_eval.restype = C.c_int
         lib.oracle_student_t_lpdf_eval.argtypes = [C.POINTER(_abi.StudentTArgs)]
+        lib.oracle_multiply.restype = C.c_int
+        lib.oracle_multiply.argtypes = [C.POINTER(_abi.MultiplyArgs)]
         lib.oracle_density_eval.restype = C.c_int
         lib.oracle_density_eval.argtypes = [C.POINTER(_abi.DensityArgs)]
         _oracle = lib
@@ -79,6 +81,11 @@ def ref_lib():
             lib.stanref_student_t_lpdf.restype = i
             lib.stanref_student_t_lpdf.argtypes = [i, i, dp, l, dp, l, dp, l, dp, l, dp, dp, dp, dp, dp, dp,
                                                    C.c_char_p, i]
+        if hasattr(lib, "stanref_multiply"):
+            lib.stanref_multiply.restype = i
+            lib.stanref_multiply.argtypes = [l, l, l, dp, dp, dp, dp, C.c_char_p, i]
+            lib.stanref_multiply_rev.restype = i
+            lib.stanref_multiply_rev.argtypes = [l, l, l, dp, dp, dp, i, dp, dp, dp, dp, C.c_char_p, i]
         lib.stanref_init_threads.restype = i
         lib.stanref_init_threads.argtypes = [i]
         lib.stanref_shards_create.restype = C.c_void_p
@@ -513,3 +520,54 @@ def ref_density(density, y, theta, propto=False, theta_var=True):
     if rc != 0:
         raise RefError(rc, err.value.decode())
     return {"lp": float(lp[0]), "dtheta": dth, "seconds": float(secs[0])}
+
+
+# ------------------------------------------------------------------------------------------
+# dense product
+def _fmat(a):
+    a = np.asarray(a, dtype=np.float64)
+    return np.asfortranarray(a.reshape(a.shape[0], -1) if a.ndim == 2 else a.reshape(-1, 1))
+
+
+def oracle_multiply(a, b, trans_a=False, trans_b=False):
+    """op(a) @ op(b) by the plain-C triple loop (oracle/glm_oracle.c: oracle_multiply)."""
+    a, b = _fmat(a), _fmat(b)
+    m, ka = (a.shape[1], a.shape[0]) if trans_a else a.shape
+    kb, n = (b.shape[1], b.shape[0]) if trans_b else b.shape
+    assert ka == kb
+    c = np.zeros((m, n), order="F")
+    g = _abi.MultiplyArgs()
+    g.m, g.n, g.k = m, n, ka
+    g.a, g.lda, g.trans_a = a.ctypes.data, max(a.shape[0], 1), int(trans_a)
+    g.b, g.ldb, g.trans_b = b.ctypes.data, max(b.shape[0], 1), int(trans_b)
+    g.c, g.ldc = c.ctypes.data, max(m, 1)
+    rc = oracle_lib().oracle_multiply(C.byref(g))
+    assert rc == 0
+    return c
+
+
+def ref_multiply(a, b):
+    """stan::math::multiply(A, B) of the compiled reference (double matrices: Eigen's product)."""
+    a, b = _fmat(a), _fmat(b)
+    (m, k), n = a.shape, b.shape[1]
+    c, secs = np.zeros((m, n), order="F"), np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_multiply(m, n, k, a.ctypes.data, b.ctypes.data, c.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return c, float(secs[0])
+
+
+def ref_multiply_rev(a, b, w, var_mask=3):
+    """Reverse mode through the compiled reference's multiply_mat_vari: C, dA = W B', dB = A' W for
+    f = sum(W * C); var_mask bit 0: A is a matrix of var, bit 1: B."""
+    a, b, w = _fmat(a), _fmat(b), _fmat(w)
+    (m, k), n = a.shape, b.shape[1]
+    c, da, db, secs = np.zeros((m, n), order="F"), np.zeros((m, k), order="F"), np.zeros((k, n), order="F"), np.zeros(2)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_multiply_rev(m, n, k, a.ctypes.data, b.ctypes.data, w.ctypes.data, int(var_mask), c.ctypes.data,
+                                        da.ctypes.data, db.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return {"c": c, "da": da if var_mask & 1 else None, "db": db if var_mask & 2 else None,
+            "forward_s": float(secs[0]), "grad_s": float(secs[1])}

@@ -1,0 +1,100 @@
+// oracle/ref_shim_dense.cpp -- TEST INFRASTRUCTURE, third translation unit of _ref/libstanref.so.
+//
+// The UNMODIFIED reference's dense `multiply` (stan/math/prim/mat/fun/multiply.hpp:66-83: Eigen's product, and
+// stan/math/rev/mat/fun/multiply.hpp:35-150, 225-328, 395-501, 619-633: multiply_mat_vari) behind C entry points, so
+// the parity tests can check the device product and its reverse-mode adjoints against the reference itself.
+// Compiled WITHOUT STAN_OPENCL / STAN_CUDA: the reference's CPU path.  Nothing is copied.
+#include <stan/math/rev/mat.hpp>
+
+#include <chrono>
+#include <cstring>
+#include <stdexcept>
+#include <vector>
+
+namespace {
+using stan::math::var;
+typedef Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic> matrix_d;
+typedef Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic> matrix_v;
+
+template <typename F>
+int guarded(F&& f, char* err, int errlen) {
+  int rc = 0;
+  try {
+    f();
+  } catch (const std::exception& e) {
+    if (err && errlen > 0) {
+      std::strncpy(err, e.what(), size_t(errlen) - 1);
+      err[errlen - 1] = 0;
+    }
+    rc = dynamic_cast<const std::domain_error*>(&e) ? 1 : dynamic_cast<const std::invalid_argument*>(&e) ? 2 : 3;
+  }
+  stan::math::recover_memory();
+  return rc;
+}
+
+matrix_v to_var(const matrix_d& m) {
+  matrix_v v(m.rows(), m.cols());
+  for (Eigen::Index i = 0; i < m.size(); ++i) v(i) = var(m(i));
+  return v;
+}
+}  // namespace
+
+extern "C" {
+
+// C (m x n) = A (m x k) * B (k x n), dense column-major doubles
+int stanref_multiply(long m, long n, long k, const double* a, const double* b, double* c, double* seconds, char* err,
+                     int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d A = Eigen::Map<const matrix_d>(a, m, k), B = Eigen::Map<const matrix_d>(b, k, n);
+        auto t0 = std::chrono::steady_clock::now();
+        matrix_d C = stan::math::multiply(A, B);
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        Eigen::Map<matrix_d>(c, m, n) = C;
+      },
+      err, errlen);
+}
+
+// Reverse mode: C = multiply(A, B) with A and / or B matrices of var (var_mask bit 0: A, bit 1: B), then the
+// gradient of f = sum_ij W_ij C_ij: dA = W B', dB = A' W.  seconds[0]: forward, seconds[1]: grad().
+int stanref_multiply_rev(long m, long n, long k, const double* a, const double* b, const double* w, int var_mask, double* c,
+                         double* da, double* db, double* seconds, char* err, int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d A = Eigen::Map<const matrix_d>(a, m, k), B = Eigen::Map<const matrix_d>(b, k, n);
+        Eigen::Map<const matrix_d> W(w, m, n);
+        matrix_v Av, Bv, Cv;
+        if (var_mask & 1) Av = to_var(A);
+        if (var_mask & 2) Bv = to_var(B);
+        auto t0 = std::chrono::steady_clock::now();
+        if ((var_mask & 3) == 3) Cv = stan::math::multiply(Av, Bv);
+        else if (var_mask & 1) Cv = stan::math::multiply(Av, B);
+        else if (var_mask & 2) Cv = stan::math::multiply(A, Bv);
+        else throw std::invalid_argument("stanref_multiply_rev: no variable operand");
+        auto t1 = std::chrono::steady_clock::now();
+        var f = 0;
+        {
+          std::vector<var> ops(Cv.data(), Cv.data() + Cv.size());
+          std::vector<double> grads(w, w + m * n);
+          double val = 0;
+          for (long i = 0; i < m * n; ++i) val += w[i] * Cv(i).val();
+          f = stan::math::precomputed_gradients(val, ops, grads);
+        }
+        auto t2 = std::chrono::steady_clock::now();
+        f.grad();
+        auto t3 = std::chrono::steady_clock::now();
+        if (seconds) {
+          seconds[0] = std::chrono::duration<double>(t1 - t0).count();
+          seconds[1] = std::chrono::duration<double>(t3 - t2).count();
+        }
+        for (long i = 0; i < m * n; ++i) c[i] = Cv(i).val();
+        if ((var_mask & 1) && da)
+          for (long i = 0; i < m * k; ++i) da[i] = Av(i).adj();
+        if ((var_mask & 2) && db)
+          for (long i = 0; i < k * n; ++i) db[i] = Bv(i).adj();
+      },
+      err, errlen);
+}
+
+}  // extern "C"

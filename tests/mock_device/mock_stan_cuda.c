@@ -26,6 +26,7 @@
 int oracle_glm_eval(const stan_cuda_glm_args* a);
 int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a);
 int oracle_student_t_lpdf_eval(const stan_cuda_student_t_args* a);
+int oracle_multiply(const stan_cuda_multiply_args* g);
 int oracle_density_eval(const stan_cuda_density_args* a);
 
 static __thread char tl_error[256];
@@ -169,6 +170,72 @@ int stan_cuda_density_eval(const stan_cuda_density_args* a) {
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
   TIMED(oracle_density_eval(a));
   return rc < 0 ? fail(rc, "stan_cuda_density_eval: bad argument") : rc;
+}
+
+/* dense matrices: a handle is a host array here (column-major, ld = rows) */
+struct stan_cuda_matrix {
+  int64_t rows, cols;
+  double* d;
+};
+
+int stan_cuda_matrix_create(int64_t rows, int64_t cols, stan_cuda_matrix** out) {
+  if (!out || rows < 0 || cols < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_create: bad argument");
+  stan_cuda_matrix* m = (stan_cuda_matrix*)malloc(sizeof(stan_cuda_matrix));
+  if (!m) return fail(STAN_CUDA_ERR_CUDA, "stan_cuda_matrix_create: out of memory");
+  m->rows = rows;
+  m->cols = cols;
+  m->d = (double*)calloc((size_t)(rows * cols > 0 ? rows * cols : 1), sizeof(double));
+  if (!m->d) {
+    free(m);
+    return fail(STAN_CUDA_ERR_CUDA, "stan_cuda_matrix_create: out of memory");
+  }
+  *out = m;
+  return STAN_CUDA_OK;
+}
+
+void stan_cuda_matrix_free(stan_cuda_matrix* m) {
+  if (m) {
+    free(m->d);
+    free(m);
+  }
+}
+
+int64_t stan_cuda_matrix_rows(const stan_cuda_matrix* m) { return m ? m->rows : 0; }
+int64_t stan_cuda_matrix_cols(const stan_cuda_matrix* m) { return m ? m->cols : 0; }
+
+int stan_cuda_matrix_upload(stan_cuda_matrix* m, const double* host, int64_t ld) {
+  if (!m || (!host && m->rows * m->cols > 0) || ld < m->rows) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_upload: bad argument");
+  for (int64_t j = 0; j < m->cols; ++j) memcpy(m->d + j * m->rows, host + j * ld, (size_t)m->rows * sizeof(double));
+  return STAN_CUDA_OK;
+}
+
+int stan_cuda_matrix_download(const stan_cuda_matrix* m, double* host, int64_t ld) {
+  if (!m || (!host && m->rows * m->cols > 0) || ld < m->rows) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_download: bad argument");
+  for (int64_t j = 0; j < m->cols; ++j) memcpy(host + j * ld, m->d + j * m->rows, (size_t)m->rows * sizeof(double));
+  return STAN_CUDA_OK;
+}
+
+int stan_cuda_matrix_multiply(const stan_cuda_matrix* a, int trans_a, const stan_cuda_matrix* b, int trans_b, stan_cuda_matrix* c) {
+  if (!a || !b || !c || c == a || c == b) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_multiply: bad argument");
+  stan_cuda_multiply_args g;
+  memset(&g, 0, sizeof(g));
+  g.m = trans_a ? a->cols : a->rows;
+  g.k = trans_a ? a->rows : a->cols;
+  g.n = trans_b ? b->rows : b->cols;
+  if ((trans_b ? b->cols : b->rows) != g.k) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_multiply: inner dimensions differ");
+  if (c->rows != g.m || c->cols != g.n) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_multiply: result has the wrong shape");
+  g.a = a->d; g.lda = a->rows > 0 ? a->rows : 1; g.trans_a = trans_a;
+  g.b = b->d; g.ldb = b->rows > 0 ? b->rows : 1; g.trans_b = trans_b;
+  g.c = c->d; g.ldc = c->rows > 0 ? c->rows : 1;
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  return oracle_multiply(&g);
+}
+
+int stan_cuda_multiply(const stan_cuda_multiply_args* g) {
+  if (!g) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_multiply: null args");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  TIMED(oracle_multiply(g));
+  return rc < 0 ? fail(rc, "stan_cuda_multiply: bad argument") : rc;
 }
 
 /* the product returns pinned memory of the calling thread; pageable memory serves a host-only run */

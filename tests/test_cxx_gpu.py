@@ -20,7 +20,8 @@ BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_po
             "ref_poisson_log_log_test", "ref_bernoulli_logit_test", "ref_poisson_log_test",
             "cuda_normal_distr_test", "ref_map_rect_concurrent_threads_test", "ref_map_rect_prim_test",
             "ref_map_rect_concurrent_prim_test", "ref_normal_log_test", "ref_normal_test",
-            "cuda_student_t_parity_test", "cuda_student_t_distr_test", "ref_student_t_log_test"]
+            "cuda_student_t_parity_test", "cuda_student_t_distr_test", "ref_student_t_log_test",
+            "cuda_multiply_test", "ref_multiply_test", "ref_mix_multiply_test"]
 
 
 @pytest.mark.gpu

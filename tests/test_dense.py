@@ -1,0 +1,171 @@
+"""Dense FP64 product on the device (the `multiply` hooks, stan/math/prim/mat/fun/multiply.hpp:66-83,
+stan/math/rev/mat/fun/multiply.hpp:35-150, and the matrix_cl surface they use).
+
+CPU: the oracle's triple loop against the golden vectors of the compiled reference (value and the two adjoint
+products) and against the compiled reference on fresh inputs.  GPU: stan_cuda_multiply and the matrix handle API
+through the C ABI against the goldens and the oracle on shapes around every tile edge, and at 4096^3 through
+properties that need no checker.
+
+The gate for a product is componentwise: |got - ref| <= 1e-10 * (|A| |B|)_ij, the scale to which ANY summation order
+of the same products is accurate (an entry of A B can be arbitrarily small against its own terms; the reference's
+tests for its OpenCL product use an absolute 1e-10 / 1e-12 on O(1000) values for the same reason,
+test/unit/math/rev/mat/fun/multiply_test.cpp:39-40).
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+from math_b200 import _abi
+from oracle import loader as L
+
+
+def product_error(got, ref, a, b):
+    bound = np.abs(a) @ np.abs(b)
+    bound = np.where(bound > 0, bound, 1.0)
+    return float(np.max(np.abs(np.asarray(got) - np.asarray(ref)) / bound)) if ref.size else 0.0
+
+
+@pytest.fixture(scope="session")
+def golden_mm():
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    return np.load(os.path.join(root, "tests", "golden", "dense_golden.npz"), allow_pickle=False)
+
+
+def _case(g, name):
+    p = "mm/%s/" % name
+    return {k: g[p + k] for k in ("a", "b", "w", "c", "da", "db")}
+
+
+# ------------------------------------------------------------------------------------------ CPU
+def test_struct_layout():
+    assert ctypes.sizeof(_abi.MultiplyArgs) == 8 * 3 + 8 + 8 + 4 + 4 + 8 + 8 + 8 + 8
+
+
+def test_oracle_matches_golden(golden_mm):
+    assert len(golden_mm["cases"]) >= 10
+    for name in golden_mm["cases"]:
+        c = _case(golden_mm, str(name))
+        a, b, w = c["a"], c["b"], c["w"]
+        assert product_error(L.oracle_multiply(a, b), c["c"], a, b) <= 1e-13, name
+        assert product_error(L.oracle_multiply(w, b, trans_b=True), c["da"], w, b.T) <= 1e-13, name   # dA = W B'
+        assert product_error(L.oracle_multiply(a, w, trans_a=True), c["db"], a.T, w) <= 1e-13, name   # dB = A' W
+    fx = _case(golden_mm, "fixture_2x3_3x2")
+    assert np.array_equal(fx["c"], np.array([[22.0, 28.0], [49.0, 64.0]]))
+
+
+@pytest.mark.skipif(not L.have_ref(), reason="oracle/_ref not built (needs /root/reference)")
+def test_oracle_matches_compiled_reference_on_fresh_inputs():
+    rng = np.random.default_rng(3)
+    for _ in range(6):
+        m, k, n = (int(v) for v in rng.integers(1, 150, 3))
+        a, b, w = rng.standard_normal((m, k)), rng.standard_normal((k, n)), rng.standard_normal((m, n))
+        ref = L.ref_multiply_rev(a, b, w, 3)
+        assert product_error(L.oracle_multiply(a, b), ref["c"], a, b) <= 1e-13
+        assert product_error(L.oracle_multiply(w, b, trans_b=True), ref["da"], w, b.T) <= 1e-13
+        assert product_error(L.oracle_multiply(a, w, trans_a=True), ref["db"], a.T, w) <= 1e-13
+
+
+# ------------------------------------------------------------------------------------------ GPU
+@pytest.fixture(scope="module")
+def dense():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from math_b200 import dense as d, glm
+    glm.init(1)
+    return d
+
+
+@pytest.mark.gpu
+def test_device_matches_golden(dense, golden_mm):
+    for name in golden_mm["cases"]:
+        c = _case(golden_mm, str(name))
+        a, b, w = c["a"], c["b"], c["w"]
+        assert product_error(dense.multiply_host(a, b), c["c"], a, b) <= 1e-10, name
+        assert product_error(dense.multiply_host(w, b, trans_b=True), c["da"], w, b.T) <= 1e-10, name
+        assert product_error(dense.multiply_host(a, w, trans_a=True), c["db"], a.T, w) <= 1e-10, name
+
+
+SHAPES = [(1, 1, 1), (1, 7, 1), (2, 3, 4), (63, 8, 65), (64, 7, 64), (64, 9, 64), (65, 16, 63), (127, 33, 129), (128, 128, 128),
+          (129, 130, 131), (255, 17, 257), (300, 1, 300), (1, 300, 1), (5, 1000, 3), (1000, 5, 3), (3, 5, 1000), (513, 64, 700),
+          (2048, 24, 1500)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("m,k,n", SHAPES)
+def test_device_matches_oracle_on_every_tile_edge(dense, m, k, n):
+    """shapes below, at and above the 64- and 128-wide tiles and the 8-deep K step; the last one is large enough for
+    the 128 x 128 kernel (>= 148 tiles), the others run the 64 x 64 kernel"""
+    rng = np.random.default_rng(m * 1000003 + k * 1009 + n)
+    a, b = rng.uniform(-5, 5, (m, k)), rng.uniform(-5, 5, (k, n))
+    ref = L.oracle_multiply(a, b)
+    assert product_error(dense.multiply_host(a, b), ref, a, b) <= 1e-10
+    at, bt = np.asfortranarray(a.T), np.asfortranarray(b.T)
+    assert product_error(dense.multiply_host(at, b, trans_a=True), ref, a, b) <= 1e-10
+    assert product_error(dense.multiply_host(a, bt, trans_b=True), ref, a, b) <= 1e-10
+    assert product_error(dense.multiply_host(at, bt, trans_a=True, trans_b=True), ref, a, b) <= 1e-10
+
+
+@pytest.mark.gpu
+def test_handle_api(dense):
+    rng = np.random.default_rng(8)
+    a, b = rng.standard_normal((150, 70)), rng.standard_normal((70, 90))
+    da, db = dense.MatrixCuda(a), dense.MatrixCuda(b)
+    assert da.shape == (150, 70) and da.T.shape == (70, 150)
+    assert np.array_equal(da.to_host(), a) and np.array_equal(da.T.to_host(), a.T)
+    ref = L.oracle_multiply(a, b)
+    c = da @ db
+    assert c.shape == (150, 90) and product_error(c.to_host(), ref, a, b) <= 1e-10
+    # the products of the reverse sweep from resident operands: adjA = W B', adjB = A' W
+    w = rng.standard_normal((150, 90))
+    dw = dense.MatrixCuda(w)
+    assert product_error((dw @ db.T).to_host(), L.oracle_multiply(w, b, trans_b=True), w, b.T) <= 1e-10
+    assert product_error((da.T @ dw).to_host(), L.oracle_multiply(a, w, trans_a=True), a.T, w) <= 1e-10
+    with pytest.raises(ValueError, match="must match in size"):
+        da @ da
+    with pytest.raises(Exception):   # the ABI refuses a result of the wrong shape / an aliased result
+        from math_b200._lib import check, lib
+        check(lib().stan_cuda_matrix_multiply(da._h, 0, db._h, 0, da._h))
+    empty = dense.MatrixCuda(np.zeros((0, 4)))
+    assert empty.to_host().shape == (0, 4)
+    z = dense.MatrixCuda(np.zeros((5, 0))) @ dense.MatrixCuda(np.zeros((0, 6)))   # empty inner dimension: zeros
+    assert z.shape == (5, 6) and not z.to_host().any()
+
+
+@pytest.mark.gpu
+def test_results_repeat_bitwise_and_do_not_depend_on_the_tiling(dense):
+    """every entry is one FMA chain over k ascending, whichever kernel and tile owns it: a column block of the product
+    equals the product with that column block of B bit for bit (here the full product runs the 128-wide kernel and
+    the block the 64-wide one), and two calls agree bit for bit"""
+    rng = np.random.default_rng(21)
+    a, b = rng.standard_normal((2000, 300)), rng.standard_normal((300, 1800))
+    full = dense.multiply_host(a, b)
+    assert np.array_equal(full, dense.multiply_host(a, b))
+    assert np.array_equal(full[:, 100:260], dense.multiply_host(a, b[:, 100:260]))
+    assert np.array_equal(full[37:100, :], dense.multiply_host(a[37:100, :], b))
+
+
+@pytest.mark.gpu
+def test_full_size_properties(dense):
+    """4096^3 (137 GFLOP: minutes for the oracle's triple loop): (A B) x = A (B x) for random x, A I = A exactly,
+    A (B + B2) = A B + A B2 to rounding, and a sampled block against the oracle."""
+    rng = np.random.default_rng(5)
+    n = 4096
+    a, b = rng.standard_normal((n, n)), rng.standard_normal((n, n))
+    da, db = dense.MatrixCuda(a), dense.MatrixCuda(b)
+    c = (da @ db).to_host()
+    x = rng.standard_normal(n)
+    lhs, rhs = c @ x, a @ (b @ x)
+    scale = np.abs(a) @ (np.abs(b) @ np.abs(x))
+    assert np.max(np.abs(lhs - rhs) / scale) <= 1e-10
+    eye = dense.MatrixCuda(np.eye(n))
+    assert np.array_equal((da @ eye).to_host(), a)
+    rows, cols = rng.integers(0, n, 24), rng.integers(0, n, 24)
+    block_ref = L.oracle_multiply(a[rows, :], b[:, cols])
+    assert product_error(c[np.ix_(rows, cols)], block_ref, a[rows, :], b[:, cols]) <= 1e-10
+    b2 = rng.standard_normal((n, n))
+    c2 = (da @ dense.MatrixCuda(b2)).to_host()
+    csum = (da @ dense.MatrixCuda(b + b2)).to_host()
+    assert product_error(csum, c + c2, a, np.abs(b) + np.abs(b2)) <= 1e-10
