@@ -9,14 +9,16 @@
 // Storage: column-major like Eigen and matrix_cl, leading dimension = rows rounded up to 16 doubles (128 B) so that
 // every column starts on a 128-byte line and the kernels can use 16-byte loads; the pad rows are zero.
 //
-// Product: C = op(A) * op(B) in FP64 on the DFMA pipe.  On B200 the FP64 tensor rate equals the vector rate
-// (~64 DFMA / clk / SM), so this is a classic register-tiled kernel rather than a DMMA one: a CTA of 256 threads owns
-// a BM x BN tile of C, walks K in steps of BK = 8 through two shared-memory stages (the global loads of step t + 1
-// are issued before the arithmetic of step t and stored after it: one barrier per step), and each thread
-// accumulates a TM x TN block in registers.  op(A) must be M-contiguous and op(B) K-contiguous (plain column-major
-// A and B); a transposed operand is first transposed on the device (2 x its bytes of HBM traffic against 2 M N K
-// flops: noise for any shape worth sending here).  The roofline is the FP64 issue rate, not HBM.
+// Product: C = op(A) * op(B) in FP64 on the tensor cores' FP64 path (mma.sync m8n8k4 f64, SASS DMMA): a CTA of 256
+// threads owns a BM x BN tile of C, walks K in steps of BK = 8 through two shared-memory stages, and each warp
+// accumulates a (BM / 2) x (BN / 4) tile as 8 x 8 DMMA fragments in registers (dgemm_nn_kernel below).  The kernel
+// takes plain column-major A and B; a transposed operand is first transposed on the device (2 x its bytes of HBM
+// traffic against 2 M N K flops: noise for any shape worth sending here).  The roofline is the FP64 rate
+// (64 FMA / clk / SM), not HBM.
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <string>
 
 #include "context.cuh"
 
@@ -57,47 +59,67 @@ __global__ void __launch_bounds__(256) transpose_kernel(const double* __restrict
 }
 
 // ---- C = A * B, column-major, A: M x K (ld lda), B: K x N (ld ldb), C: M x N (ld ldc) ----------------------
-// Thread layout: tx = tid % (BM / TMH) along M, ty = tid / (BM / TMH) along N, where a thread owns rows
-// {tx * 4 .. tx * 4 + 3} (+ BM / 2 for the second half when TM == 8) and the columns likewise.
-template <int BM, int BN, int TM, int TN>
-__global__ void __launch_bounds__(kGemmThreads, TM == 8 ? 1 : 2)
+// D(8x8) += A(8x4) * B(4x8), FP64 (SASS DMMA).  Fragments (PTX ISA, mma.m8n8k4 .f64): a = A[lane / 4][lane % 4],
+// b = B[lane % 4][lane / 4], {d0, d1} = D[lane / 4][2 * (lane % 4) + {0, 1}].
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
+}
+
+// Why DMMA although its peak equals the DFMA peak on this chip: operand delivery.  A register-tiled DFMA kernel
+// with 8 x 8 accumulators per thread reads 128 B of shared memory per thread and K step for 64 FMA -- with four
+// resident warps per SM that is exactly the 128 B / clk the shared-memory pipe moves, and the first version of this
+// kernel sat at 57 % of the FP64 pipe with the LSU saturated (profiles/r02_ncu_dgemm_simt_4096.txt).  A warp that
+// owns a 64 x 32 tile as 8 x 4 DMMA fragments reads 12 doubles per thread for 32 DMMAs (256 FMA per thread): a
+// fifth of the traffic per flop.
+//
+// CTA: 8 warps as 2 (M) x 4 (N); warp tile WM x WN = (BM / 2) x (BN / 4).  Shared stages (two, BK = 8 deep):
+//   As[k][m], row stride BM + 4 doubles: the four k of an A fragment land 8 banks apart -> conflict-free LDS.64
+//   Bs[n][k], row stride 12 doubles (8 used): the natural layout of a column-major B tile, 16-byte stores, and the
+//             rows of a B fragment land 24 banks apart -> conflict-free LDS.64
+// The global loads of stage t + 1 are issued before the DMMAs of stage t and stored after them: one barrier per
+// stage.  Every element of C is one chain of fused multiply-adds over k ascending, whichever tile owns it.
+template <int BM, int BN, int WARPS_M, int MIN_CTAS>
+__global__ void __launch_bounds__(kGemmThreads, MIN_CTAS)
 dgemm_nn_kernel(int64_t M, int64_t N, int64_t K, const double* __restrict__ A, int64_t lda, const double* __restrict__ B,
                 int64_t ldb, double* __restrict__ C, int64_t ldc) {
-  static_assert((BM / TM) * (BN / TN) == kGemmThreads, "one thread per TM x TN block");
-  static_assert(TM % 4 == 0 && TN % 4 == 0, "blocks of four");
-  constexpr int LDB_S = BN + 2;                       // +2: the transposing stores of the B tile hit distinct banks
+  constexpr int WARPS_N = kGemmThreads / 32 / WARPS_M;
+  constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;  // warp tile
+  constexpr int TM = WM / 8, TN = WN / 8;             // DMMA fragments per warp tile
+  constexpr int SA = BM + 4;                          // row stride of As
+  constexpr int SB = 12;                              // row stride of Bs
   constexpr int LA = BM * kBK / kGemmThreads;         // doubles of the A tile per thread (contiguous along M)
   constexpr int LB = BN * kBK / kGemmThreads;         // doubles of the B tile per thread (contiguous along K)
   static_assert(LA == 2 || LA == 4, "A tile: one or two 16-byte loads per thread");
   static_assert(LB == 2 || LB == 4, "B tile: one or two 16-byte loads per thread");
-  __shared__ __align__(16) double As[2][kBK][BM];
-  __shared__ __align__(16) double Bs[2][kBK][LDB_S];
+  __shared__ __align__(16) double As[2][kBK][SA];
+  __shared__ __align__(16) double Bs[2][BN][SB];
 
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t m0 = int64_t(blockIdx.x) * BM, n0 = int64_t(blockIdx.y) * BN;
   // global -> shared assignment
-  const int a_k = tid / (BM / LA), a_m = (tid % (BM / LA)) * LA;  // A(m0 + a_m .. + LA - 1, k0 + a_k)
+  const int a_k = tid / (BM / LA), a_m = (tid % (BM / LA)) * LA;    // A(m0 + a_m .. + LA - 1, k0 + a_k)
   const int b_n = tid / (kBK / LB), b_k = (tid % (kBK / LB)) * LB;  // B(k0 + b_k .. + LB - 1, n0 + b_n)
-  const bool a_row_ok = m0 + a_m < M;  // rows beyond M inside the leading dimension are zero; beyond it, nothing to read
+  const bool a_row_ok = m0 + a_m < M;  // rows in [M, lda) are zero by construction; beyond lda there is nothing to read
   const bool b_col_ok = n0 + b_n < N;
   const double* a_ptr = A + (m0 + a_m);
   const double* b_ptr = B + (n0 + b_n) * ldb;
-  // compute assignment
-  constexpr int TXN = BM / TM;  // threads along M
-  const int tx = tid % TXN, ty = tid / TXN;
+  // fragment assignment
+  const int wm0 = (warp % WARPS_M) * WM, wn0 = (warp / WARPS_M) * WN;
+  const int fr = lane >> 2, fc = lane & 3;
 
-  double acc[TM][TN];
+  double acc[TM][TN][2];
 #pragma unroll
   for (int i = 0; i < TM; ++i)
 #pragma unroll
-    for (int j = 0; j < TN; ++j) acc[i][j] = 0.0;
+    for (int j = 0; j < TN; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
   double ra[LA], rb[LB];
   auto load_global = [&](int64_t k0) {
     const int64_t ka = k0 + a_k;
     if (a_row_ok && ka < K) {
-      // lda is a multiple of 16 and a_m of LA: 16-byte aligned; rows in [M, lda) are zero by construction
-      const double2* p = reinterpret_cast<const double2*>(a_ptr + ka * lda);
+      const double2* p = reinterpret_cast<const double2*>(a_ptr + ka * lda);  // lda % 16 == 0, a_m % LA == 0: aligned
 #pragma unroll
       for (int q = 0; q < LA / 2; ++q) {
         const double2 v = (m0 + a_m + 2 * q < lda) ? __ldg(p + q) : make_double2(0.0, 0.0);
@@ -110,8 +132,7 @@ dgemm_nn_kernel(int64_t M, int64_t N, int64_t K, const double* __restrict__ A, i
     }
     const int64_t kb = k0 + b_k;
     if (b_col_ok && kb < K) {
-      // rows of B in [K, ldb) are zero by construction; kb is a multiple of LB
-      const double2* p = reinterpret_cast<const double2*>(b_ptr + kb);
+      const double2* p = reinterpret_cast<const double2*>(b_ptr + kb);  // rows of B in [K, ldb) are zero by construction
 #pragma unroll
       for (int q = 0; q < LB / 2; ++q) {
         const double2 v = (kb + 2 * q < ldb) ? __ldg(p + q) : make_double2(0.0, 0.0);
@@ -128,7 +149,8 @@ dgemm_nn_kernel(int64_t M, int64_t N, int64_t K, const double* __restrict__ A, i
     for (int q = 0; q < LA / 2; ++q)
       *reinterpret_cast<double2*>(&As[buf][a_k][a_m + 2 * q]) = make_double2(ra[2 * q], ra[2 * q + 1]);
 #pragma unroll
-    for (int q = 0; q < LB; ++q) Bs[buf][b_k + q][b_n] = rb[q];
+    for (int q = 0; q < LB / 2; ++q)
+      *reinterpret_cast<double2*>(&Bs[buf][b_n][b_k + 2 * q]) = make_double2(rb[2 * q], rb[2 * q + 1]);
   };
 
   const int64_t steps = (K + kBK - 1) / kBK;
@@ -139,70 +161,206 @@ dgemm_nn_kernel(int64_t M, int64_t N, int64_t K, const double* __restrict__ A, i
     const int buf = int(t & 1);
     if (t + 1 < steps) load_global((t + 1) * kBK);
 #pragma unroll
-    for (int kk = 0; kk < kBK; ++kk) {
+    for (int ks = 0; ks < kBK; ks += 4) {
       double a[TM], b[TN];
 #pragma unroll
-      for (int h = 0; h < TM / 4; ++h) {
-        const double2 v0 = *reinterpret_cast<const double2*>(&As[buf][kk][h * (BM / 2) + tx * 4]);
-        const double2 v1 = *reinterpret_cast<const double2*>(&As[buf][kk][h * (BM / 2) + tx * 4 + 2]);
-        a[h * 4] = v0.x; a[h * 4 + 1] = v0.y; a[h * 4 + 2] = v1.x; a[h * 4 + 3] = v1.y;
-      }
+      for (int i = 0; i < TM; ++i) a[i] = As[buf][ks + fc][wm0 + i * 8 + fr];
 #pragma unroll
-      for (int h = 0; h < TN / 4; ++h) {
-        const double2 v0 = *reinterpret_cast<const double2*>(&Bs[buf][kk][h * (BN / 2) + ty * 4]);
-        const double2 v1 = *reinterpret_cast<const double2*>(&Bs[buf][kk][h * (BN / 2) + ty * 4 + 2]);
-        b[h * 4] = v0.x; b[h * 4 + 1] = v0.y; b[h * 4 + 2] = v1.x; b[h * 4 + 3] = v1.y;
-      }
+      for (int j = 0; j < TN; ++j) b[j] = Bs[buf][wn0 + j * 8 + fr][ks + fc];
 #pragma unroll
       for (int i = 0; i < TM; ++i)
 #pragma unroll
-        for (int j = 0; j < TN; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < TN; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
     if (t + 1 < steps) store_shared(buf ^ 1);
     __syncthreads();
   }
 
-  // epilogue: four consecutive rows per (half, column) -> two 16-byte stores
+  // epilogue: fragment (i, j) holds C[m0 + wm0 + i * 8 + fr][n0 + wn0 + j * 8 + 2 * fc + {0, 1}]
 #pragma unroll
-  for (int hj = 0; hj < TN / 4; ++hj)
+  for (int i = 0; i < TM; ++i) {
+    const int64_t m = m0 + wm0 + i * 8 + fr;
+    if (m >= M) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int64_t n = n0 + hj * (BN / 2) + ty * 4 + j;
-      if (n >= N) continue;
-#pragma unroll
-      for (int hi = 0; hi < TM / 4; ++hi) {
-        const int64_t m = m0 + hi * (BM / 2) + tx * 4;
-        double* c = C + n * ldc + m;
-        const int r = hi * 4, cj = hj * 4 + j;  // rows r .. r + 3 of column cj of the thread's block
-        if (m + 3 < M) {
-          *reinterpret_cast<double2*>(c) = make_double2(acc[r][cj], acc[r + 1][cj]);
-          *reinterpret_cast<double2*>(c + 2) = make_double2(acc[r + 2][cj], acc[r + 3][cj]);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (m + i < M) c[i] = acc[r + i][cj];
-        }
-      }
+    for (int j = 0; j < TN; ++j) {
+      const int64_t n = n0 + wn0 + j * 8 + 2 * fc;
+      if (n < N) C[n * ldc + m] = acc[i][j][0];
+      if (n + 1 < N) C[(n + 1) * ldc + m] = acc[i][j][1];
     }
+  }
 }
 
-template <int BM, int BN, int TM, int TN>
+template <int BM, int BN, int WARPS_M, int MIN_CTAS>
 int launch_dgemm(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb, double* C,
                  int64_t ldc, cudaStream_t stream) {
   const int64_t gx = (M + BM - 1) / BM, gy = (N + BN - 1) / BN;
   if (gy > 65535) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_multiply: more than 65535 column tiles");
-  dgemm_nn_kernel<BM, BN, TM, TN><<<dim3(unsigned(gx), unsigned(gy)), kGemmThreads, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc);
+  dgemm_nn_kernel<BM, BN, WARPS_M, MIN_CTAS><<<dim3(unsigned(gx), unsigned(gy)), kGemmThreads, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc);
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
 }
 
+// Tile variants.  0: 128 x 128, warps 2 x 4 (64 x 32 each), one CTA per SM.  1: 128 x 64, warps 4 x 2 (32 x 32 each),
+// two CTAs per SM: while one CTA waits at its stage barrier the other keeps the DMMA pipe busy.  2: 64 x 64 for
+// products with fewer tiles than SMs.  STAN_CUDA_GEMM_TILE=0|1|2 forces one (for measurements); every variant gives
+// the same bits (same FMA chain per element).
+int gemm_tile_override() {
+  static const int v = [] {
+    const char* e = getenv("STAN_CUDA_GEMM_TILE");
+    return e ? atoi(e) : -1;
+  }();
+  return v;
+}
+
 int dgemm_nn(int device, int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb, double* C,
              int64_t ldc, cudaStream_t stream) {
-  // 128 x 128 tiles when they fill the machine at least once, 64 x 64 below that
-  const int64_t big_tiles = ((M + 127) / 128) * ((N + 127) / 128);
-  if (big_tiles >= sm_count(device)) return launch_dgemm<128, 128, 8, 8>(M, N, K, A, lda, B, ldb, C, ldc, stream);
-  return launch_dgemm<64, 64, 4, 4>(M, N, K, A, lda, B, ldb, C, ldc, stream);
+  int variant = gemm_tile_override();
+  if (variant < 0 || variant > 2) {
+    const int64_t tiles = ((M + 127) / 128) * ((N + 63) / 64);
+    variant = tiles >= 2 * int64_t(sm_count(device)) ? 1 : 2;
+  }
+  if (variant == 0) return launch_dgemm<128, 128, 2, 1>(M, N, K, A, lda, B, ldb, C, ldc, stream);
+  if (variant == 1) return launch_dgemm<128, 64, 4, 2>(M, N, K, A, lda, B, ldb, C, ldc, stream);
+  return launch_dgemm<64, 64, 2, 2>(M, N, K, A, lda, B, ldb, C, ldc, stream);
+}
+
+// ---- host <-> device copies of a rows x cols column-major block ---------------------------------------------
+// Copies from / to PAGEABLE host memory crawl on this platform: 0.75 GB/s measured for a 134 MB matrix, 1-D or 2-D
+// alike (profiles/r02_gemm_timing_*.jsonl), against > 20 GB/s from page-locked memory.  Eigen's and the autodiff
+// arena's memory is pageable, so every block larger than a few pages goes through two page-locked staging buffers
+// of the calling thread: the CPU packs (unpacks) one chunk while the DMA engine moves the other.
+// STAN_CUDA_DENSE_COPY=direct restores the plain cudaMemcpy path (for measuring the difference).
+struct CopyStage {
+  double* buf[2] = {nullptr, nullptr};
+  cudaEvent_t done[2] = {nullptr, nullptr};
+  size_t cap = 0;  // doubles per buffer
+  ~CopyStage() {
+    for (int q = 0; q < 2; ++q) {
+      if (buf[q]) cudaFreeHost(buf[q]);
+      if (done[q]) cudaEventDestroy(done[q]);
+    }
+  }
+};
+constexpr size_t kStageDoubles = size_t(1) << 20;  // 8 MiB per buffer
+constexpr int64_t kDirectCopyDoubles = 8192;       // blocks up to 64 KiB: one plain copy
+
+int copy_stage(CopyStage** out) {
+  static thread_local CopyStage st;
+  if (!st.buf[0]) {
+    for (int q = 0; q < 2; ++q) {
+      SC_CUDA(cudaMallocHost(reinterpret_cast<void**>(&st.buf[q]), kStageDoubles * sizeof(double)));
+      SC_CUDA(cudaEventCreateWithFlags(&st.done[q], cudaEventDisableTiming));
+    }
+    st.cap = kStageDoubles;
+  }
+  *out = &st;
+  return STAN_CUDA_OK;
+}
+
+bool direct_copies() {
+  static const bool direct = [] {
+    const char* e = getenv("STAN_CUDA_DENSE_COPY");
+    return e && std::string(e) == "direct";
+  }();
+  return direct;
+}
+
+// One chunk = `nc` pieces of `len` doubles, `host_stride` apart on the host and `dev_stride` apart on the device.
+// Walks the block in chunks that fit a staging buffer; `to_device` selects the direction.  Device -> host returns
+// with the data in place (the stream is synchronised).
+int staged_copy(bool to_device, double* dev, int64_t ld_dev, double* host, int64_t ld_host, int64_t rows, int64_t cols,
+                cudaStream_t stream) {
+  CopyStage* st;
+  SC_TRY(copy_stage(&st));
+  const int64_t cap = int64_t(st->cap);
+  const int64_t piece = std::min(rows, cap);                         // doubles of one column handled at a time
+  const int64_t pieces_per_col = (rows + piece - 1) / piece;
+  const int64_t cols_per_chunk = pieces_per_col == 1 ? std::max<int64_t>(1, cap / rows) : 1;
+  struct Chunk { int64_t j0, nc, r0, len; int q; };
+  auto dma = [&](const Chunk& c) -> int {
+    double* d = dev + c.j0 * ld_dev + c.r0;
+    const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    if (to_device) {
+      SC_CUDA(cudaMemcpy2DAsync(d, size_t(ld_dev) * sizeof(double), st->buf[c.q], size_t(c.len) * sizeof(double),
+                                size_t(c.len) * sizeof(double), size_t(c.nc), kind, stream));
+    } else {
+      SC_CUDA(cudaMemcpy2DAsync(st->buf[c.q], size_t(c.len) * sizeof(double), d, size_t(ld_dev) * sizeof(double),
+                                size_t(c.len) * sizeof(double), size_t(c.nc), kind, stream));
+    }
+    SC_CUDA(cudaEventRecord(st->done[c.q], stream));
+    return STAN_CUDA_OK;
+  };
+  auto cpu_side = [&](const Chunk& c) -> int {  // pack before the DMA (to device) or unpack after it (to host)
+    SC_CUDA(cudaEventSynchronize(st->done[c.q]));
+    for (int64_t j = 0; j < c.nc; ++j) {
+      double* h = host + (c.j0 + j) * ld_host + c.r0;
+      double* b = st->buf[c.q] + j * c.len;
+      if (to_device) memcpy(b, h, size_t(c.len) * sizeof(double));
+      else memcpy(h, b, size_t(c.len) * sizeof(double));
+    }
+    return STAN_CUDA_OK;
+  };
+  bool have_pending = false;
+  Chunk pending{};
+  int q = 0;
+  for (int64_t j0 = 0; j0 < cols; j0 += cols_per_chunk)
+    for (int64_t r0 = 0; r0 < rows; r0 += piece) {
+      Chunk c{j0, std::min(cols_per_chunk, cols - j0), r0, std::min(piece, rows - r0), q};
+      q ^= 1;
+      if (to_device) {
+        SC_TRY(cpu_side(c));  // waits for the DMA that last read this buffer, then packs
+        SC_TRY(dma(c));
+      } else {
+        SC_TRY(dma(c));       // buffer c.q was unpacked one iteration ago
+        if (have_pending) SC_TRY(cpu_side(pending));
+        pending = c;
+        have_pending = true;
+      }
+    }
+  if (!to_device) {
+    if (have_pending) SC_TRY(cpu_side(pending));
+    SC_CUDA(cudaStreamSynchronize(stream));
+  }
+  return STAN_CUDA_OK;
+}
+
+int copy_to_device(double* dev, int64_t ld_dev, const double* host, int64_t ld_host, int64_t rows, int64_t cols, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return STAN_CUDA_OK;
+  const bool contiguous = cols == 1 || (ld_dev == rows && ld_host == rows);
+  if (rows * cols <= kDirectCopyDoubles || direct_copies()) {
+    if (contiguous) {
+      SC_CUDA(cudaMemcpyAsync(dev, host, size_t(rows) * size_t(cols) * sizeof(double), cudaMemcpyHostToDevice, stream));
+    } else {
+      SC_CUDA(cudaMemcpy2DAsync(dev, size_t(ld_dev) * sizeof(double), host, size_t(ld_host) * sizeof(double),
+                                size_t(rows) * sizeof(double), size_t(cols), cudaMemcpyHostToDevice, stream));
+    }
+    return STAN_CUDA_OK;
+  }
+  if (contiguous) return staged_copy(true, dev, rows * cols, const_cast<double*>(host), rows * cols, rows * cols, 1, stream);
+  return staged_copy(true, dev, ld_dev, const_cast<double*>(host), ld_host, rows, cols, stream);
+}
+
+// returns with the data in `host` (synchronises the stream)
+int copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) {
+    SC_CUDA(cudaStreamSynchronize(stream));
+    return STAN_CUDA_OK;
+  }
+  const bool contiguous = cols == 1 || (ld_dev == rows && ld_host == rows);
+  if (rows * cols <= kDirectCopyDoubles || direct_copies()) {
+    if (contiguous) {
+      SC_CUDA(cudaMemcpyAsync(host, dev, size_t(rows) * size_t(cols) * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    } else {
+      SC_CUDA(cudaMemcpy2DAsync(host, size_t(ld_host) * sizeof(double), dev, size_t(ld_dev) * sizeof(double),
+                                size_t(rows) * sizeof(double), size_t(cols), cudaMemcpyDeviceToHost, stream));
+    }
+    SC_CUDA(cudaStreamSynchronize(stream));
+    return STAN_CUDA_OK;
+  }
+  double* d = const_cast<double*>(dev);
+  if (contiguous) return staged_copy(false, d, rows * cols, host, rows * cols, rows * cols, 1, stream);
+  return staged_copy(false, d, ld_dev, host, ld_host, rows, cols, stream);
 }
 
 int use_device_of(const stan_cuda_matrix* m, ThreadDev** td) {
@@ -280,8 +438,7 @@ int matrix_upload(stan_cuda_matrix* m, const double* host, int64_t ld) {
   NvtxRange range("stan_cuda_matrix_upload");
   ThreadDev* td;
   SC_TRY(use_device_of(m, &td));
-  SC_CUDA(cudaMemcpy2DAsync(m->d, size_t(m->ld) * sizeof(double), host, size_t(ld) * sizeof(double), size_t(m->rows) * sizeof(double),
-                            size_t(m->cols), cudaMemcpyHostToDevice, td->stream));
+  SC_TRY(copy_to_device(m->d, m->ld, host, ld, m->rows, m->cols, td->stream));
   SC_CUDA(cudaStreamSynchronize(td->stream));
   counters().bytes_uploaded.fetch_add(uint64_t(m->rows) * uint64_t(m->cols) * sizeof(double));
   return STAN_CUDA_OK;
@@ -294,9 +451,7 @@ int matrix_download(const stan_cuda_matrix* m, double* host, int64_t ld) {
   NvtxRange range("stan_cuda_matrix_download");
   ThreadDev* td;
   SC_TRY(use_device_of(m, &td));
-  SC_CUDA(cudaMemcpy2DAsync(host, size_t(ld) * sizeof(double), m->d, size_t(m->ld) * sizeof(double), size_t(m->rows) * sizeof(double),
-                            size_t(m->cols), cudaMemcpyDeviceToHost, td->stream));
-  SC_CUDA(cudaStreamSynchronize(td->stream));
+  SC_TRY(copy_to_host(host, ld, m->d, m->ld, m->rows, m->cols, td->stream));
   return STAN_CUDA_OK;
 }
 
@@ -367,20 +522,14 @@ int multiply_host(const stan_cuda_multiply_args* g) {
   if (rc >= 0) rc = matrix_create_on(dev, g->m, g->n, false, &c);
   auto copy_in = [&](stan_cuda_matrix* m, const double* host, int64_t ld) -> int {
     if (m->rows == 0 || m->cols == 0) return STAN_CUDA_OK;
-    SC_CUDA(cudaMemcpy2DAsync(m->d, size_t(m->ld) * sizeof(double), host, size_t(ld) * sizeof(double), size_t(m->rows) * sizeof(double),
-                              size_t(m->cols), cudaMemcpyHostToDevice, td->stream));
+    SC_TRY(copy_to_device(m->d, m->ld, host, ld, m->rows, m->cols, td->stream));
     counters().bytes_uploaded.fetch_add(uint64_t(m->rows) * uint64_t(m->cols) * sizeof(double));
     return STAN_CUDA_OK;
   };
   if (rc >= 0) rc = copy_in(a, g->a, g->lda);
   if (rc >= 0) rc = copy_in(b, g->b, g->ldb);
   if (rc >= 0) rc = matrix_multiply(a, g->trans_a, b, g->trans_b, c, false);
-  if (rc >= 0) {
-    cudaError_t e = cudaMemcpy2DAsync(g->c, size_t(g->ldc) * sizeof(double), c->d, size_t(c->ld) * sizeof(double),
-                                      size_t(g->m) * sizeof(double), size_t(g->n), cudaMemcpyDeviceToHost, td->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(td->stream);
-    if (e != cudaSuccess) rc = fail_cuda(e, "download of the product", __FILE__, __LINE__);
-  }
+  if (rc >= 0) rc = copy_to_host(g->c, g->ldc, c->d, c->ld, g->m, g->n, td->stream);
   if (a) matrix_free(a);
   if (b) matrix_free(b);
   if (c) matrix_free(c);
