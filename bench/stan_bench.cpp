@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|s1|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|s1|m1|m2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -382,6 +382,40 @@ double student_t_once(const VectorXd& y, double nu_val, const VectorXd& mu_val, 
   return t1 - t0;
 }
 
+// dense multiply.  prim: C = multiply(A, B) for double matrices; rev: AB = multiply(A_v, B_v) with
+// both operands matrices of var, f = sum(AB), grad() and the adjoints of A and B read back (forward + the two
+// products of chain()).
+template <bool GPU>
+double multiply_prim_once(const MatrixXd& A, const MatrixXd& B, Result* out) {
+  const double t0 = now();
+  MatrixXd C = GPU ? stan::math::multiply(A, B) : stan::math::multiply_reference_cpu(A, B);
+  const double t1 = now();
+  out->lp = C.sum();
+  out->grad = Eigen::Map<VectorXd>(C.data(), std::min<int64_t>(C.size(), 4096));
+  return t1 - t0;
+}
+
+template <bool GPU>
+double multiply_rev_once(const MatrixXd& A, const MatrixXd& B, Result* out) {
+  using namespace stan::math;  // NOLINT
+  typedef Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic> matrix_v;
+  start_nested();
+  matrix_v Av(A.rows(), A.cols()), Bv(B.rows(), B.cols());
+  for (int64_t i = 0; i < A.size(); ++i) Av(i) = A(i);
+  for (int64_t i = 0; i < B.size(); ++i) Bv(i) = B(i);
+  const double t0 = now();
+  matrix_v AB = GPU ? multiply(Av, Bv) : multiply_reference_cpu(Av, Bv);
+  var f = sum(AB);
+  grad(f.vi_);
+  out->lp = f.val();
+  out->grad.resize(A.size() + B.size());
+  for (int64_t i = 0; i < A.size(); ++i) out->grad[i] = Av(i).adj();
+  for (int64_t i = 0; i < B.size(); ++i) out->grad[A.size() + i] = Bv(i).adj();
+  const double t1 = now();
+  recover_memory_nested();
+  return t1 - t0;
+}
+
 // vectorised lpmf with an integer outcome and a var vector operand (DENSITY 1: bernoulli_logit_lpmf,
 // 2: poisson_log_lpmf); one evaluation = forward + grad() + reading the N adjoints
 template <bool GPU, int DENSITY>
@@ -494,6 +528,33 @@ int run(int argc, char** argv) {
       std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
     }
     std::printf(", \"algorithmic_device_bytes\": %lld}\n", (long long)(3 * n * 8));
+    return 0;
+  }
+
+  if (config == "m1" || config == "m2") {
+    const bool rev = config == "m2";
+    const int64_t n = n_override ? n_override : (rev ? 1024 : 2048);
+    MatrixXd A(n, n), B(n, n);
+    Rng r(1031);
+    for (int64_t i = 0; i < n * n; ++i) {
+      A(i) = r.normal();
+      B(i) = r.normal();
+    }
+    Result g, c;
+    auto gpu = [&] { return rev ? multiply_rev_once<true>(A, B, &g) : multiply_prim_once<true>(A, B, &g); };
+    auto cpu = [&] { return rev ? multiply_rev_once<false>(A, B, &c) : multiply_prim_once<false>(A, B, &c); };
+    gpu();
+    Timing tg = time_reps(2, reps, 30, gpu);
+    std::printf("\"what\": \"multiply %lld x %lld x %lld, %s\", ", (long long)n, (long long)n, (long long)n,
+                rev ? "matrices of var: forward + grad() + reading the adjoints" : "matrices of double");
+    print_timing("gpu", tg);
+    if (!no_cpu) {
+      Timing tc = time_reps(0, std::max(std::min(cpu_reps, 3), 2), 60, cpu);
+      std::printf(", ");
+      print_timing("cpu_reference_1_thread", tc);
+      std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
+    }
+    std::printf(", \"flops\": %.6g}\n", (rev ? 6.0 : 2.0) * double(n) * double(n) * double(n));
     return 0;
   }
 

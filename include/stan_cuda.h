@@ -83,6 +83,7 @@ extern "C" {
 #define STAN_CUDA_BAD_OUTCOME 2
 #define STAN_CUDA_BAD_OPERAND 3
 #define STAN_CUDA_LOG_ZERO 4
+#define STAN_CUDA_NOT_POS_DEF 5 /* cholesky_decompose: a pivot is not positive (matrix not positive definite, or NaN) */
 #define STAN_CUDA_ERR_ARG (-1)
 #define STAN_CUDA_ERR_CUDA (-2)
 #define STAN_CUDA_ERR_NCCL (-3)
@@ -327,6 +328,18 @@ STAN_CUDA_API int stan_cuda_matrix_download(const stan_cuda_matrix* m, double* h
 STAN_CUDA_API int stan_cuda_matrix_multiply(const stan_cuda_matrix* a, int trans_a, const stan_cuda_matrix* b, int trans_b,
                                             stan_cuda_matrix* c);
 STAN_CUDA_API int stan_cuda_multiply(const stan_cuda_multiply_args* a);
+/* Cholesky factor and its reverse-mode adjoint (the cholesky_decompose hooks of
+ * stan/math/prim/mat/fun/cholesky_decompose.hpp:34-62 and stan/math/rev/mat/fun/cholesky_decompose.hpp:255-440, for
+ * which the OpenCL backend has opencl::cholesky_decompose, stan/math/opencl/cholesky_decompose.hpp:36-107, and
+ * cholesky_opencl::chain()).  Host matrices, column-major.
+ * decompose: l (n x n) = lower Cholesky factor of a (its lower triangle is read), zeros above the diagonal.  Returns
+ *   STAN_CUDA_NOT_POS_DEF when a pivot is not positive -- the wrapper then runs the reference's LLT +
+ *   check_pos_definite on the host to throw the identical exception.
+ * adjoint: given l and the adjoints l_adj of its lower triangle, writes the adjoints of the lower triangle of a into
+ *   a_adj (n x n; the strict upper triangle of a_adj is not meaningful). */
+STAN_CUDA_API int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl);
+STAN_CUDA_API int stan_cuda_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj,
+                                             double* a_adj, int64_t lda);
 /* Page-locked staging memory of the calling thread (at least `bytes`, valid until the thread's next
  * call with a larger size).  Operands gathered into it upload by DMA without a bounce buffer. */
 STAN_CUDA_API void* stan_cuda_host_staging(size_t bytes);

@@ -1,0 +1,311 @@
+// cholesky.cu -- Cholesky factorisation and its reverse-mode adjoint on the device.
+//
+// Replaces, for the cholesky_decompose hooks of the reference (stan/math/prim/mat/fun/cholesky_decompose.hpp:34-62,
+// stan/math/rev/mat/fun/cholesky_decompose.hpp:255-383, 396-440), what its OpenCL backend provides there:
+// opencl::cholesky_decompose (stan/math/opencl/cholesky_decompose.hpp:36-107: blocked, diagonal block factorised by
+// one work-group, panel by tri_inverse + multiply, trailing matrix by multiply_transpose) and the blocked reverse
+// sweep of cholesky_opencl::chain() (rev/mat/fun/cholesky_decompose.hpp:329-382; same algebra as the CPU
+// cholesky_block::chain(), :120-167 -- Murray 2016, "Differentiation of the Cholesky decomposition").
+//
+// Forward, lower triangular, blocks of NB = 64 columns; A is consumed, L is written to a second matrix:
+//   1. potrf_inv_kernel   one CTA: L_D = chol(D) for the 64 x 64 diagonal block in shared memory, and W = L_D^-1
+//   2. dgemm (N, T)       panel     L[j+64:, j:j+64] = A[j+64:, j:j+64] * W'
+//   3. dgemm (N, T), lower-only     A[j+64:, j+64:] -= panel * panel'
+// Reverse, blocks from the bottom up (the block boundaries are multiples of 64 from the top: any blocking is valid
+// and this one keeps every sub-block 16-byte aligned):
+//   W = D^-1 (tri_inv_kernel);  Cb = Cb W;  Bb -= Cb R;  Db -= Cb' C;  Db = sym(D, W, Db) (symbolic_rev_kernel);
+//   Rb -= Cb' B + Db_sym R;  diag(Db) *= 1/2.
+// The products are the DMMA kernel of gemm.cu on sub-blocks; the three small kernels run one CTA each and are the
+// serial spine of both sweeps (n / 64 steps).
+#include <algorithm>
+
+#include "context.cuh"
+
+namespace stancuda {
+
+int scope_device_ordinal();  // api.cu
+
+namespace {
+
+constexpr int kNB = 64;          // block size of both sweeps
+constexpr int kLD = kNB + 1;     // row stride of the 64 x 64 blocks in shared memory (bank spread)
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ double& at(double* m, int r, int c) { return m[r * kLD + c]; }
+
+// W = inverse of the lower-triangular jb x jb matrix Lm (both in shared memory, W zero above the diagonal).
+// Thread c solves L x = e_c by forward substitution: at every step all threads read the same L(i, k) row segment.
+__device__ void tri_inverse_shared(const double* Lm, double* W, int jb, int tid) {
+  for (int idx = tid; idx < kNB * kNB; idx += kThreads) at(W, idx / kNB, idx % kNB) = 0.0;
+  __syncthreads();
+  if (tid < jb) {
+    const int c = tid;
+    at(W, c, c) = 1.0 / Lm[c * kLD + c];
+    for (int i = c + 1; i < jb; ++i) {
+      double s = 0.0;
+      for (int k = c; k < i; ++k) s = fma(Lm[i * kLD + k], at(W, k, c), s);
+      at(W, i, c) = -s / Lm[i * kLD + i];
+    }
+  }
+  __syncthreads();
+}
+
+// load the lower triangle of a jb x jb block (zero elsewhere, zero padding up to 64 x 64)
+__device__ void load_lower(double* dst, const double* src, int64_t ld, int jb, int tid) {
+  for (int idx = tid; idx < kNB * kNB; idx += kThreads) {
+    const int r = idx % kNB, c = idx / kNB;
+    at(dst, r, c) = (r < jb && c <= r) ? src[int64_t(c) * ld + r] : 0.0;
+  }
+}
+
+// step 1 of the forward sweep.  info: 0, or 1 + the index of the first pivot that is not positive (NaN included)
+__global__ void __launch_bounds__(kThreads) potrf_inv_kernel(const double* __restrict__ A, int64_t lda, int jb, int64_t j0,
+                                                            double* __restrict__ L, int64_t ldl, double* __restrict__ W,
+                                                            int* __restrict__ info) {
+  extern __shared__ double sm[];
+  double* D = sm;
+  double* Wm = sm + kNB * kLD;
+  __shared__ int failed;
+  const int tid = threadIdx.x;
+  if (*info != 0) return;  // an earlier block failed: nothing below it is meaningful
+  if (tid == 0) failed = 0;
+  load_lower(D, A, lda, jb, tid);
+  for (int j = 0; j < jb; ++j) {
+    __syncthreads();
+    const double pivot = at(D, j, j);
+    if (!(pivot > 0.0)) {  // uniform: every thread reads the same value
+      if (tid == 0) {
+        *info = int(j0) + j + 1;
+        failed = 1;
+      }
+      break;
+    }
+    const double ljj = sqrt(pivot);
+    __syncthreads();  // everyone has the pivot before it is overwritten
+    for (int i = j + tid; i < jb; i += kThreads) at(D, i, j) = (i == j) ? ljj : at(D, i, j) / ljj;
+    __syncthreads();
+    const int nt = jb - j - 1;
+    for (int idx = tid; idx < nt * nt; idx += kThreads) {
+      const int r = j + 1 + idx % nt, c = j + 1 + idx / nt;
+      if (r >= c) at(D, r, c) = fma(-at(D, r, j), at(D, c, j), at(D, r, c));
+    }
+  }
+  __syncthreads();
+  if (failed) return;
+  tri_inverse_shared(D, Wm, jb, tid);
+  for (int idx = tid; idx < jb * jb; idx += kThreads) {
+    const int r = idx % jb, c = idx / jb;
+    if (r >= c) L[int64_t(c) * ldl + r] = at(D, r, c);
+  }
+  for (int idx = tid; idx < kNB * kNB; idx += kThreads) W[idx] = at(Wm, idx % kNB, idx / kNB);  // column-major, ld = 64
+}
+
+// W = D^-1 for a lower-triangular diagonal block of L (reverse sweep)
+__global__ void __launch_bounds__(kThreads) tri_inv_kernel(const double* __restrict__ Dg, int64_t ld, int jb, double* __restrict__ W) {
+  extern __shared__ double sm[];
+  double* D = sm;
+  double* Wm = sm + kNB * kLD;
+  const int tid = threadIdx.x;
+  load_lower(D, Dg, ld, jb, tid);
+  __syncthreads();
+  tri_inverse_shared(D, Wm, jb, tid);
+  for (int idx = tid; idx < kNB * kNB; idx += kThreads) W[idx] = at(Wm, idx % kNB, idx / kNB);
+}
+
+// out = X' * Y or X * Y for 64 x 64 blocks in shared memory; thread (tx, ty) of a 16 x 16 grid owns a 4 x 4 block
+template <bool TRANS_X>
+__device__ void block_product(const double* X, const double* Y, double* out, int tid) {
+  const int r0 = (tid % 16) * 4, c0 = (tid / 16) * 4;
+  double acc[4][4] = {};
+  for (int k = 0; k < kNB; ++k) {
+    double x[4], y[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x[i] = TRANS_X ? X[k * kLD + r0 + i] : X[(r0 + i) * kLD + k];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) y[j] = Y[k * kLD + c0 + j];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = fma(x[i], y[j], acc[i][j]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) out[(r0 + i) * kLD + c0 + j] = acc[i][j];
+}
+
+// symbolic_rev (rev/mat/fun/cholesky_decompose.hpp:102-112 / :301-307): with P = tril(Db),
+//   Phi = symmetrised lower triangle of D' P;   Db_sym = D^-T Phi D^-1 = W' Phi W.
+// Writes Db_sym (full, column-major, ld = 64) for the update of R and, into the adjoint matrix, its lower triangle with
+// the diagonal halved (:160-161).
+__global__ void __launch_bounds__(kThreads) symbolic_rev_kernel(const double* __restrict__ Dg, int64_t ldd, const double* __restrict__ Wg,
+                                                               double* __restrict__ Db, int64_t ldb, int jb, double* __restrict__ Dsym) {
+  extern __shared__ double sm[];
+  double* D = sm;
+  double* W = sm + kNB * kLD;
+  double* P = sm + 2 * kNB * kLD;
+  double* T = sm + 3 * kNB * kLD;
+  const int tid = threadIdx.x;
+  load_lower(D, Dg, ldd, jb, tid);
+  load_lower(P, Db, ldb, jb, tid);
+  for (int idx = tid; idx < kNB * kNB; idx += kThreads) at(W, idx % kNB, idx / kNB) = Wg[idx];
+  __syncthreads();
+  block_product<true>(D, P, T, tid);  // T = D' P
+  __syncthreads();
+  for (int idx = tid; idx < kNB * kNB; idx += kThreads) {
+    const int r = idx / kNB, c = idx % kNB;
+    at(P, r, c) = r >= c ? at(T, r, c) : at(T, c, r);  // Phi
+  }
+  __syncthreads();
+  block_product<false>(P, W, T, tid);  // T = Phi W
+  __syncthreads();
+  block_product<true>(W, T, P, tid);   // P = W' T
+  __syncthreads();
+  for (int idx = tid; idx < kNB * kNB; idx += kThreads) {
+    const int r = idx % kNB, c = idx / kNB;
+    Dsym[idx] = at(P, r, c);
+    if (r < jb && c < jb && r >= c) Db[int64_t(c) * ldb + r] = (r == c ? 0.5 : 1.0) * at(P, r, c);
+  }
+}
+
+struct DeviceBuf {
+  double* p = nullptr;
+  cudaStream_t stream = nullptr;
+  ~DeviceBuf() {
+    if (p) cudaFreeAsync(p, stream);
+  }
+  int alloc(size_t doubles, cudaStream_t s) {
+    stream = s;
+    SC_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&p), std::max<size_t>(doubles, 2) * sizeof(double), s));
+    return STAN_CUDA_OK;
+  }
+};
+
+int64_t padded(int64_t n) { return n <= 0 ? 16 : (n + 15) / 16 * 16; }
+
+int set_smem_limits() {  // per device (the attribute belongs to the function on the current device): cheap, every call
+  SC_CUDA(cudaFuncSetAttribute(symbolic_rev_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(4 * kNB * kLD * sizeof(double))));
+  SC_CUDA(cudaFuncSetAttribute(potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(2 * kNB * kLD * sizeof(double))));
+  SC_CUDA(cudaFuncSetAttribute(tri_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(2 * kNB * kLD * sizeof(double))));
+  return STAN_CUDA_OK;
+}
+
+}  // namespace
+
+// host <-> device block copies through page-locked staging (gemm.cu)
+int dense_copy_to_device(double* dev, int64_t ld_dev, const double* host, int64_t ld_host, int64_t rows, int64_t cols, cudaStream_t stream);
+int dense_copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols, cudaStream_t stream);
+
+// A (n x n, its lower triangle is read) is consumed; L receives the factor (zeros above the diagonal).  *info_host: 0
+// or 1 + index of the first non-positive pivot.
+int cholesky_device(int dev, double* A, double* L, int64_t ld, int64_t n, int* info_dev, double* W, cudaStream_t stream) {
+  SC_TRY(set_smem_limits());
+  const size_t smem2 = 2 * kNB * kLD * sizeof(double);
+  for (int64_t j = 0; j < n; j += kNB) {
+    const int jb = int(std::min<int64_t>(kNB, n - j));
+    const int64_t m = n - j - jb;
+    potrf_inv_kernel<<<1, kThreads, smem2, stream>>>(A + j + j * ld, ld, jb, j, L + j + j * ld, ld, W, info_dev);
+    SC_CUDA(cudaGetLastError());
+    counters().launches.fetch_add(1, std::memory_order_relaxed);
+    if (m > 0) {
+      // panel = A_panel * W'  (m x jb) ; trailing -= panel * panel' (lower)
+      SC_TRY(dgemm(dev, false, true, false, m, jb, jb, 1.0, A + (j + jb) + j * ld, ld, W, kNB, 0.0, L + (j + jb) + j * ld, ld, stream));
+      SC_TRY(dgemm(dev, false, true, true, m, m, jb, -1.0, L + (j + jb) + j * ld, ld, L + (j + jb) + j * ld, ld, 1.0,
+                   A + (j + jb) + (j + jb) * ld, ld, stream));
+    }
+  }
+  return STAN_CUDA_OK;
+}
+
+int cholesky_host(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {
+  NvtxRange range("stan_cuda_cholesky_decompose");
+  if (n < 0 || (n > 0 && (!a || !l || lda < n || ldl < n))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_cholesky_decompose: bad argument");
+  if (n == 0) return STAN_CUDA_OK;
+  SC_TRY(ensure_init());
+  const int dev = scope_device_ordinal();
+  ThreadDev* td;
+  SC_TRY(thread_dev(dev, &td));
+  SC_CUDA(cudaSetDevice(dev));
+  const int64_t ld = padded(n);
+  DeviceBuf A, L, W, info;
+  SC_TRY(A.alloc(size_t(ld) * n, td->stream));
+  SC_TRY(L.alloc(size_t(ld) * n, td->stream));
+  SC_TRY(W.alloc(kNB * kNB, td->stream));
+  SC_TRY(info.alloc(2, td->stream));
+  SC_CUDA(cudaMemsetAsync(L.p, 0, size_t(ld) * n * sizeof(double), td->stream));
+  SC_CUDA(cudaMemsetAsync(info.p, 0, 2 * sizeof(double), td->stream));
+  SC_TRY(dense_copy_to_device(A.p, ld, a, lda, n, n, td->stream));
+  counters().bytes_uploaded.fetch_add(uint64_t(n) * uint64_t(n) * sizeof(double));
+  SC_TRY(cholesky_device(dev, A.p, L.p, ld, n, reinterpret_cast<int*>(info.p), W.p, td->stream));
+  SC_TRY(td->reserve_host(8));
+  SC_CUDA(cudaMemcpyAsync(td->h_pinned, info.p, sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  SC_TRY(dense_copy_to_host(l, ldl, L.p, ld, n, n, td->stream));  // synchronises
+  counters().evals.fetch_add(1, std::memory_order_relaxed);
+  const int info_host = *reinterpret_cast<const int*>(td->h_pinned);
+  return info_host != 0 ? STAN_CUDA_NOT_POS_DEF : STAN_CUDA_OK;
+}
+
+// a_adj (lower triangle, n x n) = adjoint of A given L and the adjoint of L (lower triangles are read)
+int cholesky_adjoint_host(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda) {
+  NvtxRange range("stan_cuda_cholesky_adjoint");
+  if (n < 0 || (n > 0 && (!l || !l_adj || !a_adj || ldl < n || ldadj < n || lda < n)))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_cholesky_adjoint: bad argument");
+  if (n == 0) return STAN_CUDA_OK;
+  SC_TRY(ensure_init());
+  SC_TRY(set_smem_limits());
+  const int dev = scope_device_ordinal();
+  ThreadDev* td;
+  SC_TRY(thread_dev(dev, &td));
+  SC_CUDA(cudaSetDevice(dev));
+  cudaStream_t s = td->stream;
+  const int64_t ld = padded(n);
+  DeviceBuf L, Lb, W, Dsym, Tmp;
+  SC_TRY(L.alloc(size_t(ld) * n, s));
+  SC_TRY(Lb.alloc(size_t(ld) * n, s));
+  SC_TRY(W.alloc(kNB * kNB, s));
+  SC_TRY(Dsym.alloc(kNB * kNB, s));
+  SC_TRY(Tmp.alloc(size_t(ld) * kNB, s));
+  SC_TRY(dense_copy_to_device(L.p, ld, l, ldl, n, n, s));
+  SC_TRY(dense_copy_to_device(Lb.p, ld, l_adj, ldadj, n, n, s));
+  counters().bytes_uploaded.fetch_add(2 * uint64_t(n) * uint64_t(n) * sizeof(double));
+  const size_t smem2 = 2 * kNB * kLD * sizeof(double), smem4 = 4 * kNB * kLD * sizeof(double);
+  const int64_t nblk = (n + kNB - 1) / kNB;
+  for (int64_t b = nblk - 1; b >= 0; --b) {
+    const int64_t j = b * kNB, k = std::min<int64_t>(n, j + kNB);
+    const int kj = int(k - j);
+    const int64_t mk = n - k;
+    double *D = L.p + j + j * ld, *R = L.p + j, *B = L.p + k, *C = L.p + k + j * ld;
+    double *Db = Lb.p + j + j * ld, *Rb = Lb.p + j, *Bb = Lb.p + k, *Cb = Lb.p + k + j * ld;
+    tri_inv_kernel<<<1, kThreads, smem2, s>>>(D, ld, kj, W.p);
+    SC_CUDA(cudaGetLastError());
+    if (mk > 0) {
+      // Cb = Cb D^-1                                                         (:147-151 / :358)
+      SC_TRY(dgemm(dev, false, false, false, mk, kj, kj, 1.0, Cb, ld, W.p, kNB, 0.0, Tmp.p, ld, s));
+      SC_CUDA(cudaMemcpy2DAsync(Cb, size_t(ld) * sizeof(double), Tmp.p, size_t(ld) * sizeof(double), size_t(mk) * sizeof(double),
+                                size_t(kj), cudaMemcpyDeviceToDevice, s));
+      if (j > 0) SC_TRY(dgemm(dev, false, false, false, mk, j, kj, -1.0, Cb, ld, R, ld, 1.0, Bb, ld, s));  // Bb -= Cb R   (:152 / :359)
+      SC_TRY(dgemm(dev, true, false, false, kj, kj, mk, -1.0, Cb, ld, C, ld, 1.0, Db, ld, s));            // Db -= Cb' C  (:153 / :360)
+    }
+    symbolic_rev_kernel<<<1, kThreads, smem4, s>>>(D, ld, W.p, Db, ld, kj, Dsym.p);                         // :155 / :362
+    SC_CUDA(cudaGetLastError());
+    counters().launches.fetch_add(2, std::memory_order_relaxed);
+    if (j > 0) {
+      if (mk > 0) SC_TRY(dgemm(dev, true, false, false, kj, j, mk, -1.0, Cb, ld, B, ld, 1.0, Rb, ld, s));  // Rb -= Cb' B   (:156 / :364)
+      SC_TRY(dgemm(dev, false, false, false, kj, j, kj, -1.0, Dsym.p, kNB, R, ld, 1.0, Rb, ld, s));        // Rb -= Db_sym R (:157 / :364)
+    }
+  }
+  SC_TRY(dense_copy_to_host(a_adj, lda, Lb.p, ld, n, n, s));  // the caller reads the lower triangle
+  counters().evals.fetch_add(1, std::memory_order_relaxed);
+  return STAN_CUDA_OK;
+}
+
+}  // namespace stancuda
+
+extern "C" {
+int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {
+  return stancuda::cholesky_host(n, a, lda, l, ldl);
+}
+int stan_cuda_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda) {
+  return stancuda::cholesky_adjoint_host(n, l, ldl, l_adj, ldadj, a_adj, lda);
+}
+}

@@ -198,6 +198,10 @@ struct NormalIO {
 };
 int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream_t stream);
 
+// dense FP64 product on raw device pointers (gemm.cu): C = alpha * op(A) * op(B) + beta * C, column-major
+int dgemm(int device, bool trans_a, bool trans_b, bool lower_only, int64_t M, int64_t N, int64_t K, double alpha, const double* A,
+          int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc, cudaStream_t stream);
+
 // student_t_lpdf kernel (student_t.cu)
 struct StudentTIO {
   uint32_t flags;

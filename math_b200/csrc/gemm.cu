@@ -11,10 +11,9 @@
 //
 // Product: C = op(A) * op(B) in FP64 on the tensor cores' FP64 path (mma.sync m8n8k4 f64, SASS DMMA): a CTA of 256
 // threads owns a BM x BN tile of C, walks K in steps of BK = 8 through two shared-memory stages, and each warp
-// accumulates a (BM / 2) x (BN / 4) tile as 8 x 8 DMMA fragments in registers (dgemm_nn_kernel below).  The kernel
-// takes plain column-major A and B; a transposed operand is first transposed on the device (2 x its bytes of HBM
-// traffic against 2 M N K flops: noise for any shape worth sending here).  The roofline is the FP64 rate
-// (64 FMA / clk / SM), not HBM.
+// accumulates its part of the tile as 8 x 8 DMMA fragments in registers (dgemm_kernel below).  Either operand may be
+// transposed: the shared-memory layout of its tile follows its storage order, no transposed copy is made.  The
+// roofline is the FP64 rate (64 FMA / clk / SM), not HBM.
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -39,28 +38,9 @@ constexpr int kBK = 8;
 
 inline int64_t padded_ld(int64_t rows) { return rows <= 0 ? 16 : (rows + 15) / 16 * 16; }
 
-// ---- transpose: out(c, r) = in(r, c); 32 x 32 tiles through shared memory ---------------------------------
-__global__ void __launch_bounds__(256) transpose_kernel(const double* __restrict__ in, int64_t ld_in, int64_t rows, int64_t cols,
-                                                        double* __restrict__ out, int64_t ld_out) {
-  __shared__ double tile[32][33];
-  const int64_t r0 = int64_t(blockIdx.x) * 32, c0 = int64_t(blockIdx.y) * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-#pragma unroll
-  for (int j = 0; j < 32; j += 8) {
-    const int64_t r = r0 + tx, c = c0 + ty + j;
-    tile[ty + j][tx] = (r < rows && c < cols) ? in[c * ld_in + r] : 0.0;
-  }
-  __syncthreads();
-#pragma unroll
-  for (int j = 0; j < 32; j += 8) {
-    const int64_t c = c0 + tx, r = r0 + ty + j;  // element (r, c) of `in` goes to out(c, r)
-    if (r < rows && c < cols) out[r * ld_out + c] = tile[tx][ty + j];
-  }
-}
-
-// ---- C = A * B, column-major, A: M x K (ld lda), B: K x N (ld ldb), C: M x N (ld ldc) ----------------------
-// D(8x8) += A(8x4) * B(4x8), FP64 (SASS DMMA).  Fragments (PTX ISA, mma.m8n8k4 .f64): a = A[lane / 4][lane % 4],
-// b = B[lane % 4][lane / 4], {d0, d1} = D[lane / 4][2 * (lane % 4) + {0, 1}].
+// ---- C = alpha * op(A) * op(B) + beta * C, column-major ------------------------------------------------------
+// D(8x8) += A(8x4) * B(4x8), FP64 (SASS DMMA.8x8x4 -- every f64 mma shape lowers to it on sm_100a).  Fragments (PTX
+// ISA, mma.m8n8k4 .f64): a = A[lane / 4][lane % 4], b = B[lane % 4][lane / 4], {d0, d1} = D[lane / 4][2 * (lane % 4) + {0, 1}].
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
                : "+d"(d0), "+d"(d1)
@@ -74,38 +54,79 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // owns a 64 x 32 tile as 8 x 4 DMMA fragments reads 12 doubles per thread for 32 DMMAs (256 FMA per thread): a
 // fifth of the traffic per flop.
 //
-// CTA: 8 warps as 2 (M) x 4 (N); warp tile WM x WN = (BM / 2) x (BN / 4).  Shared stages (two, BK = 8 deep):
-//   As[k][m], row stride BM + 4 doubles: the four k of an A fragment land 8 banks apart -> conflict-free LDS.64
-//   Bs[n][k], row stride 12 doubles (8 used): the natural layout of a column-major B tile, 16-byte stores, and the
-//             rows of a B fragment land 24 banks apart -> conflict-free LDS.64
+// CTA: 8 warps as WARPS_M x (8 / WARPS_M); shared stages (two, BK = 8 deep), one layout per storage order of the
+// operand so that no transposed copy is ever made:
+//   "long" layout  T[k][x], row stride BX + 4 doubles -- for an operand whose M (resp. N) index is contiguous in
+//                  memory (A not transposed, B transposed): 16-byte stores; the four k of a fragment land 8 banks
+//                  apart -> conflict-free LDS.64
+//   "deep" layout  T[x][k], row stride 12 doubles (8 used) -- for an operand whose K index is contiguous (A
+//                  transposed, B not transposed): 16-byte stores; the rows of a fragment land 24 banks apart ->
+//                  conflict-free LDS.64
 // The global loads of stage t + 1 are issued before the DMMAs of stage t and stored after them: one barrier per
 // stage.  Every element of C is one chain of fused multiply-adds over k ascending, whichever tile owns it.
-template <int BM, int BN, int WARPS_M, int MIN_CTAS>
+// LOWER_ONLY skips the tiles strictly above the diagonal (the symmetric rank-k updates of the Cholesky routines).
+template <int BX, bool DEEP>
+struct OperandTile {
+  static constexpr int kStride = DEEP ? 12 : BX + 4;
+  static constexpr int kDoubles = DEEP ? BX * 12 : kBK * (BX + 4);
+  static constexpr int kPerThread = BX * kBK / kGemmThreads;  // 2 or 4 contiguous doubles
+  static_assert(kPerThread == 2 || kPerThread == 4, "one or two 16-byte loads per thread");
+  // which (x, k) a thread loads: `kPerThread` consecutive elements along the contiguous index
+  __device__ static int x_of(int tid) { return DEEP ? tid / (kBK / kPerThread) : (tid % (BX / kPerThread)) * kPerThread; }
+  __device__ static int k_of(int tid) { return DEEP ? (tid % (kBK / kPerThread)) * kPerThread : tid / (BX / kPerThread); }
+  __device__ static int offset(int x, int k) { return DEEP ? x * 12 + k : k * (BX + 4) + x; }
+  // global element (x, k) of op(P): P[x + k * ld] when x is contiguous, P[k + x * ld] when k is
+  __device__ static void load(const double* __restrict__ P, int64_t ld, int64_t x0, int64_t X, int64_t k0, int64_t K, int tid,
+                              double* r) {
+    const int64_t x = x0 + x_of(tid), k = k0 + k_of(tid);
+#pragma unroll
+    for (int q = 0; q < kPerThread; ++q) r[q] = 0.0;
+    if (DEEP) {
+      if (x >= X) return;
+      const double* p = P + x * ld + k;
+#pragma unroll
+      for (int q = 0; q < kPerThread; q += 2) {
+        if (k + q < K) {
+          const double2 v = __ldg(reinterpret_cast<const double2*>(p + q));
+          r[q] = v.x;
+          r[q + 1] = (k + q + 1 < K) ? v.y : 0.0;
+        }
+      }
+    } else {
+      if (k >= K) return;
+      const double* p = P + k * ld + x;
+#pragma unroll
+      for (int q = 0; q < kPerThread; q += 2) {
+        if (x + q < X) {
+          const double2 v = __ldg(reinterpret_cast<const double2*>(p + q));
+          r[q] = v.x;
+          r[q + 1] = (x + q + 1 < X) ? v.y : 0.0;
+        }
+      }
+    }
+  }
+  __device__ static void store(double* T, int tid, const double* r) {
+    double* t = T + offset(x_of(tid), k_of(tid));
+#pragma unroll
+    for (int q = 0; q < kPerThread; q += 2) *reinterpret_cast<double2*>(t + q) = make_double2(r[q], r[q + 1]);
+  }
+};
+
+template <int BM, int BN, int WARPS_M, int MIN_CTAS, bool TA, bool TB, bool LOWER_ONLY>
 __global__ void __launch_bounds__(kGemmThreads, MIN_CTAS)
-dgemm_nn_kernel(int64_t M, int64_t N, int64_t K, const double* __restrict__ A, int64_t lda, const double* __restrict__ B,
-                int64_t ldb, double* __restrict__ C, int64_t ldc) {
+dgemm_kernel(int64_t M, int64_t N, int64_t K, double alpha, const double* __restrict__ A, int64_t lda, const double* __restrict__ B,
+             int64_t ldb, double beta, double* __restrict__ C, int64_t ldc) {
   constexpr int WARPS_N = kGemmThreads / 32 / WARPS_M;
   constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;  // warp tile
-  constexpr int TM = WM / 8, TN = WN / 8;             // DMMA fragments per warp tile
-  constexpr int SA = BM + 4;                          // row stride of As
-  constexpr int SB = 12;                              // row stride of Bs
-  constexpr int LA = BM * kBK / kGemmThreads;         // doubles of the A tile per thread (contiguous along M)
-  constexpr int LB = BN * kBK / kGemmThreads;         // doubles of the B tile per thread (contiguous along K)
-  static_assert(LA == 2 || LA == 4, "A tile: one or two 16-byte loads per thread");
-  static_assert(LB == 2 || LB == 4, "B tile: one or two 16-byte loads per thread");
-  __shared__ __align__(16) double As[2][kBK][SA];
-  __shared__ __align__(16) double Bs[2][BN][SB];
+  constexpr int TM = WM / 8, TN = WN / 8;              // DMMA fragments per warp tile
+  typedef OperandTile<BM, TA> TileA;                   // A transposed: K contiguous -> deep
+  typedef OperandTile<BN, !TB> TileB;                  // B not transposed: K contiguous -> deep
+  const int64_t m0 = int64_t(blockIdx.x) * BM, n0 = int64_t(blockIdx.y) * BN;
+  if (LOWER_ONLY && n0 >= m0 + BM) return;             // every element of the tile has n > m
+  __shared__ __align__(16) double As[2][TileA::kDoubles];
+  __shared__ __align__(16) double Bs[2][TileB::kDoubles];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int64_t m0 = int64_t(blockIdx.x) * BM, n0 = int64_t(blockIdx.y) * BN;
-  // global -> shared assignment
-  const int a_k = tid / (BM / LA), a_m = (tid % (BM / LA)) * LA;    // A(m0 + a_m .. + LA - 1, k0 + a_k)
-  const int b_n = tid / (kBK / LB), b_k = (tid % (kBK / LB)) * LB;  // B(k0 + b_k .. + LB - 1, n0 + b_n)
-  const bool a_row_ok = m0 + a_m < M;  // rows in [M, lda) are zero by construction; beyond lda there is nothing to read
-  const bool b_col_ok = n0 + b_n < N;
-  const double* a_ptr = A + (m0 + a_m);
-  const double* b_ptr = B + (n0 + b_n) * ldb;
-  // fragment assignment
   const int wm0 = (warp % WARPS_M) * WM, wn0 = (warp / WARPS_M) * WN;
   const int fr = lane >> 2, fc = lane & 3;
 
@@ -115,87 +136,65 @@ dgemm_nn_kernel(int64_t M, int64_t N, int64_t K, const double* __restrict__ A, i
 #pragma unroll
     for (int j = 0; j < TN; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-  double ra[LA], rb[LB];
-  auto load_global = [&](int64_t k0) {
-    const int64_t ka = k0 + a_k;
-    if (a_row_ok && ka < K) {
-      const double2* p = reinterpret_cast<const double2*>(a_ptr + ka * lda);  // lda % 16 == 0, a_m % LA == 0: aligned
-#pragma unroll
-      for (int q = 0; q < LA / 2; ++q) {
-        const double2 v = (m0 + a_m + 2 * q < lda) ? __ldg(p + q) : make_double2(0.0, 0.0);
-        ra[2 * q] = v.x;
-        ra[2 * q + 1] = v.y;
-      }
-    } else {
-#pragma unroll
-      for (int q = 0; q < LA; ++q) ra[q] = 0.0;
-    }
-    const int64_t kb = k0 + b_k;
-    if (b_col_ok && kb < K) {
-      const double2* p = reinterpret_cast<const double2*>(b_ptr + kb);  // rows of B in [K, ldb) are zero by construction
-#pragma unroll
-      for (int q = 0; q < LB / 2; ++q) {
-        const double2 v = (kb + 2 * q < ldb) ? __ldg(p + q) : make_double2(0.0, 0.0);
-        rb[2 * q] = v.x;
-        rb[2 * q + 1] = v.y;
-      }
-    } else {
-#pragma unroll
-      for (int q = 0; q < LB; ++q) rb[q] = 0.0;
-    }
-  };
-  auto store_shared = [&](int buf) {
-#pragma unroll
-    for (int q = 0; q < LA / 2; ++q)
-      *reinterpret_cast<double2*>(&As[buf][a_k][a_m + 2 * q]) = make_double2(ra[2 * q], ra[2 * q + 1]);
-#pragma unroll
-    for (int q = 0; q < LB / 2; ++q)
-      *reinterpret_cast<double2*>(&Bs[buf][b_n][b_k + 2 * q]) = make_double2(rb[2 * q], rb[2 * q + 1]);
-  };
-
+  double ra[TileA::kPerThread], rb[TileB::kPerThread];
   const int64_t steps = (K + kBK - 1) / kBK;
-  load_global(0);
-  store_shared(0);
+  TileA::load(A, lda, m0, M, 0, K, tid, ra);
+  TileB::load(B, ldb, n0, N, 0, K, tid, rb);
+  TileA::store(As[0], tid, ra);
+  TileB::store(Bs[0], tid, rb);
   __syncthreads();
   for (int64_t t = 0; t < steps; ++t) {
     const int buf = int(t & 1);
-    if (t + 1 < steps) load_global((t + 1) * kBK);
+    if (t + 1 < steps) {
+      TileA::load(A, lda, m0, M, (t + 1) * kBK, K, tid, ra);
+      TileB::load(B, ldb, n0, N, (t + 1) * kBK, K, tid, rb);
+    }
 #pragma unroll
     for (int ks = 0; ks < kBK; ks += 4) {
       double a[TM], b[TN];
 #pragma unroll
-      for (int i = 0; i < TM; ++i) a[i] = As[buf][ks + fc][wm0 + i * 8 + fr];
+      for (int i = 0; i < TM; ++i) a[i] = As[buf][TileA::offset(wm0 + i * 8 + fr, ks + fc)];
 #pragma unroll
-      for (int j = 0; j < TN; ++j) b[j] = Bs[buf][wn0 + j * 8 + fr][ks + fc];
+      for (int j = 0; j < TN; ++j) b[j] = Bs[buf][TileB::offset(wn0 + j * 8 + fr, ks + fc)];
 #pragma unroll
       for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < TN; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
-    if (t + 1 < steps) store_shared(buf ^ 1);
+    if (t + 1 < steps) {
+      TileA::store(As[buf ^ 1], tid, ra);
+      TileB::store(Bs[buf ^ 1], tid, rb);
+    }
     __syncthreads();
   }
 
   // epilogue: fragment (i, j) holds C[m0 + wm0 + i * 8 + fr][n0 + wn0 + j * 8 + 2 * fc + {0, 1}]
+  const bool plain = alpha == 1.0 && beta == 0.0;
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
     const int64_t m = m0 + wm0 + i * 8 + fr;
     if (m >= M) continue;
 #pragma unroll
     for (int j = 0; j < TN; ++j) {
-      const int64_t n = n0 + wn0 + j * 8 + 2 * fc;
-      if (n < N) C[n * ldc + m] = acc[i][j][0];
-      if (n + 1 < N) C[(n + 1) * ldc + m] = acc[i][j][1];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int64_t n = n0 + wn0 + j * 8 + 2 * fc + e;
+        if (n >= N || (LOWER_ONLY && n > m)) continue;
+        double* c = C + n * ldc + m;
+        if (plain) *c = acc[i][j][e];
+        else *c = beta == 0.0 ? alpha * acc[i][j][e] : fma(alpha, acc[i][j][e], beta * *c);
+      }
     }
   }
 }
 
-template <int BM, int BN, int WARPS_M, int MIN_CTAS>
-int launch_dgemm(int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb, double* C,
-                 int64_t ldc, cudaStream_t stream) {
+template <int BM, int BN, int WARPS_M, int MIN_CTAS, bool TA, bool TB, bool LOWER_ONLY>
+int launch_dgemm(int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda, const double* B, int64_t ldb,
+                 double beta, double* C, int64_t ldc, cudaStream_t stream) {
   const int64_t gx = (M + BM - 1) / BM, gy = (N + BN - 1) / BN;
-  if (gy > 65535) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_multiply: more than 65535 column tiles");
-  dgemm_nn_kernel<BM, BN, WARPS_M, MIN_CTAS><<<dim3(unsigned(gx), unsigned(gy)), kGemmThreads, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc);
+  if (gy > 65535) return fail(STAN_CUDA_ERR_ARG, "dgemm: more than 65535 column tiles");
+  dgemm_kernel<BM, BN, WARPS_M, MIN_CTAS, TA, TB, LOWER_ONLY>
+      <<<dim3(unsigned(gx), unsigned(gy)), kGemmThreads, 0, stream>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
@@ -213,17 +212,42 @@ int gemm_tile_override() {
   return v;
 }
 
-int dgemm_nn(int device, int64_t M, int64_t N, int64_t K, const double* A, int64_t lda, const double* B, int64_t ldb, double* C,
-             int64_t ldc, cudaStream_t stream) {
+template <bool TA, bool TB, bool LOWER_ONLY>
+int dgemm_variant(int device, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda, const double* B,
+                  int64_t ldb, double beta, double* C, int64_t ldc, cudaStream_t stream) {
   int variant = gemm_tile_override();
   if (variant < 0 || variant > 2) {
     const int64_t tiles = ((M + 127) / 128) * ((N + 63) / 64);
-    variant = tiles >= 2 * int64_t(sm_count(device)) ? 1 : 2;
+    variant = tiles >= 2 * int64_t(sm_count(device)) * (LOWER_ONLY ? 2 : 1) ? 1 : 2;
   }
-  if (variant == 0) return launch_dgemm<128, 128, 2, 1>(M, N, K, A, lda, B, ldb, C, ldc, stream);
-  if (variant == 1) return launch_dgemm<128, 64, 4, 2>(M, N, K, A, lda, B, ldb, C, ldc, stream);
-  return launch_dgemm<64, 64, 2, 2>(M, N, K, A, lda, B, ldb, C, ldc, stream);
+  if (variant == 0) return launch_dgemm<128, 128, 2, 1, TA, TB, LOWER_ONLY>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream);
+  if (variant == 1) return launch_dgemm<128, 64, 4, 2, TA, TB, LOWER_ONLY>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream);
+  return launch_dgemm<64, 64, 2, 2, TA, TB, LOWER_ONLY>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream);
 }
+
+}  // namespace
+
+// C (M x N) = alpha * op(A) * op(B) + beta * C on raw device pointers (sub-blocks of larger matrices included): every
+// pointer 16-byte aligned, every leading dimension even.  With lower_only only the elements with n <= m are
+// computed and written (M == N for the callers: symmetric updates).
+int dgemm(int device, bool trans_a, bool trans_b, bool lower_only, int64_t M, int64_t N, int64_t K, double alpha, const double* A,
+          int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc, cudaStream_t stream) {
+  if (M <= 0 || N <= 0) return STAN_CUDA_OK;
+  if (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) || (lda & 1) || (ldb & 1))
+    return fail(STAN_CUDA_ERR_ARG, "dgemm: operand not 16-byte aligned");
+#define STAN_CUDA_DGEMM_CASE(TA, TB)                                                                                      \
+  if (trans_a == TA && trans_b == TB)                                                                                     \
+    return lower_only ? dgemm_variant<TA, TB, true>(device, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream)          \
+                      : dgemm_variant<TA, TB, false>(device, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream);
+  STAN_CUDA_DGEMM_CASE(false, false)
+  STAN_CUDA_DGEMM_CASE(false, true)
+  STAN_CUDA_DGEMM_CASE(true, false)
+  STAN_CUDA_DGEMM_CASE(true, true)
+#undef STAN_CUDA_DGEMM_CASE
+  return STAN_CUDA_OK;
+}
+
+namespace {
 
 // ---- host <-> device copies of a rows x cols column-major block ---------------------------------------------
 // Copies from / to PAGEABLE host memory crawl on this platform: 0.75 GB/s measured for a 134 MB matrix, 1-D or 2-D
@@ -407,6 +431,13 @@ int matrix_create_on(int device, int64_t rows, int64_t cols, bool zero, stan_cud
 
 }  // namespace
 
+int dense_copy_to_device(double* dev, int64_t ld_dev, const double* host, int64_t ld_host, int64_t rows, int64_t cols, cudaStream_t stream) {
+  return copy_to_device(dev, ld_dev, host, ld_host, rows, cols, stream);
+}
+int dense_copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols, cudaStream_t stream) {
+  return copy_to_host(host, ld_host, dev, ld_dev, rows, cols, stream);
+}
+
 int matrix_create(int64_t rows, int64_t cols, stan_cuda_matrix** out) {
   if (!out) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_create: null out");
   SC_TRY(ensure_init());
@@ -475,27 +506,7 @@ int matrix_multiply(const stan_cuda_matrix* a, int trans_a, const stan_cuda_matr
     if (sync) SC_CUDA(cudaStreamSynchronize(td->stream));
     return STAN_CUDA_OK;
   }
-  stan_cuda_matrix* at = nullptr;
-  stan_cuda_matrix* bt = nullptr;
-  int rc = STAN_CUDA_OK;
-  auto transposed = [&](const stan_cuda_matrix* src, stan_cuda_matrix** dst) -> int {
-    SC_TRY(matrix_create_on(src->device, src->cols, src->rows, true, dst));
-    const dim3 grid(unsigned((src->rows + 31) / 32), unsigned((src->cols + 31) / 32));
-    if (grid.y > 65535) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_matrix_multiply: transpose of more than 2097120 columns");
-    transpose_kernel<<<grid, 256, 0, td->stream>>>(src->d, src->ld, src->rows, src->cols, (*dst)->d, (*dst)->ld);
-    SC_CUDA(cudaGetLastError());
-    counters().launches.fetch_add(1, std::memory_order_relaxed);
-    return STAN_CUDA_OK;
-  };
-  if (trans_a) rc = transposed(a, &at);
-  if (rc >= 0 && trans_b) rc = transposed(b, &bt);
-  if (rc >= 0) {
-    const stan_cuda_matrix* aa = at ? at : a;
-    const stan_cuda_matrix* bb = bt ? bt : b;
-    rc = dgemm_nn(c->device, M, N, K, aa->d, aa->ld, bb->d, bb->ld, c->d, c->ld, td->stream);
-  }
-  if (at) matrix_free(at);  // stream-ordered: freed after the product that reads it
-  if (bt) matrix_free(bt);
+  int rc = dgemm(c->device, trans_a != 0, trans_b != 0, false, M, N, K, 1.0, a->d, a->ld, b->d, b->ld, 0.0, c->d, c->ld, td->stream);
   if (rc >= 0 && sync) SC_CUDA(cudaStreamSynchronize(td->stream));
   return rc;
 }

@@ -88,3 +88,29 @@ def multiply_host(a, b, trans_a=False, trans_b=False):
     g.c, g.ldc = c.ctypes.data, max(m, 1)
     check(lib().stan_cuda_multiply(C.byref(g)))
     return c
+
+
+class NotPositiveDefinite(ValueError):
+    """cholesky_decompose: the reference throws std::domain_error ("Matrix m is not positive definite")."""
+
+
+def cholesky_decompose(a):
+    """Lower Cholesky factor of a symmetric positive-definite matrix (stan_cuda_cholesky_decompose)."""
+    a = _fmat(a)
+    if a.shape[0] != a.shape[1]:
+        raise ValueError("cholesky_decompose: Expecting a square matrix; rows of A (%d) and columns of A (%d) must match in size" % a.shape)
+    n = a.shape[0]
+    l = np.zeros((n, n), order="F")
+    rc = check(lib().stan_cuda_cholesky_decompose(n, a.ctypes.data, max(n, 1), l.ctypes.data, max(n, 1)))
+    if rc == _abi.NOT_POS_DEF:
+        raise NotPositiveDefinite("cholesky_decompose: Matrix m is not positive definite")
+    return l
+
+
+def cholesky_adjoint(l, l_adj):
+    """Reverse sweep of L = cholesky_decompose(A): the adjoint of the lower triangle of A (zeros above)."""
+    l, l_adj = _fmat(l), _fmat(l_adj)
+    n = l.shape[0]
+    out = np.zeros((n, n), order="F")
+    check(lib().stan_cuda_cholesky_adjoint(n, l.ctypes.data, max(n, 1), l_adj.ctypes.data, max(n, 1), out.ctypes.data, max(n, 1)))
+    return np.tril(out)

@@ -431,6 +431,66 @@ int oracle_multiply(const stan_cuda_multiply_args* g) {
   return STAN_CUDA_OK;
 }
 
+/* Cholesky factor, lower: what Eigen::LLT computes for the reference's cholesky_decompose
+ * (stan/math/prim/mat/fun/cholesky_decompose.hpp:34-62; rev: stan/math/rev/mat/fun/cholesky_decompose.hpp:396-405),
+ * as the textbook column algorithm.  Reads the lower triangle of a; l gets zeros above the diagonal.  NOT_POS_DEF
+ * where check_pos_definite throws (a pivot that is not positive, NaN included). */
+int oracle_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {
+  if (n < 0) return STAN_CUDA_ERR_ARG;
+  for (int64_t j = 0; j < n; ++j)
+    for (int64_t i = 0; i < n; ++i) l[j * ldl + i] = 0.0;
+  for (int64_t j = 0; j < n; ++j) {
+    double s = a[j * lda + j];
+    for (int64_t k = 0; k < j; ++k) s -= l[k * ldl + j] * l[k * ldl + j];
+    if (!(s > 0.0)) return STAN_CUDA_NOT_POS_DEF;
+    const double ljj = sqrt(s);
+    l[j * ldl + j] = ljj;
+    for (int64_t i = j + 1; i < n; ++i) {
+      double t = a[j * lda + i];
+      for (int64_t k = 0; k < j; ++k) t -= l[k * ldl + i] * l[k * ldl + j];
+      l[j * ldl + i] = t / ljj;
+    }
+  }
+  return STAN_CUDA_OK;
+}
+
+/* Reverse sweep of the Cholesky factor, unblocked: the loops of cholesky_scalar::chain()
+ * (stan/math/rev/mat/fun/cholesky_decompose.hpp:236-252), on full n x n arrays instead of the packed ones.
+ * Reads the lower triangles of l and l_adj, writes the lower triangle of a_adj (zeros above). */
+int oracle_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj,
+                            int64_t lda) {
+  if (n < 0) return STAN_CUDA_ERR_ARG;
+  double* adjL = (double*)calloc((size_t)(n * n > 0 ? n * n : 1), sizeof(double));
+  if (!adjL) return STAN_CUDA_ERR_ARG;
+#define ADJL(i, j) adjL[(j) * n + (i)]
+#define LA(i, j) l[(j) * ldl + (i)]
+  for (int64_t j = 0; j < n; ++j)
+    for (int64_t i = 0; i < n; ++i) {
+      ADJL(i, j) = i >= j ? l_adj[j * ldadj + i] : 0.0;
+      a_adj[j * lda + i] = 0.0;
+    }
+  for (int64_t i = n - 1; i >= 0; --i) {
+    for (int64_t j = i; j >= 0; --j) {
+      double adjA;
+      if (i == j) {
+        adjA = 0.5 * ADJL(i, j) / LA(i, j);                                  /* :239-240 */
+      } else {
+        adjA = ADJL(i, j) / LA(j, j);                                        /* :242 */
+        ADJL(j, j) -= ADJL(i, j) * LA(i, j) / LA(j, j);                      /* :243-244 */
+      }
+      for (int64_t k = j - 1; k >= 0; --k) {                                 /* :246-249 */
+        ADJL(i, k) -= adjA * LA(j, k);
+        ADJL(j, k) -= adjA * LA(i, k);
+      }
+      a_adj[j * lda + i] = adjA;                                             /* :250 */
+    }
+  }
+#undef ADJL
+#undef LA
+  free(adjL);
+  return STAN_CUDA_OK;
+}
+
 /* Vectorised elementwise densities with an integer outcome.
  *   bernoulli_logit_lpmf  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
  *   poisson_log_lpmf      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93

@@ -41,6 +41,11 @@ def oracle_lib():
         lib.oracle_normal_lpdf_eval.argtypes = [C.POINTER(_abi.NormalArgs)]
         lib.oracle_student_t_lpdf_eval.restype = C.c_int
         lib.oracle_student_t_lpdf_eval.argtypes = [C.POINTER(_abi.StudentTArgs)]
+        i64, vp_ = C.c_int64, C.c_void_p
+        lib.oracle_cholesky_decompose.restype = C.c_int
+        lib.oracle_cholesky_decompose.argtypes = [i64, vp_, i64, vp_, i64]
+        lib.oracle_cholesky_adjoint.restype = C.c_int
+        lib.oracle_cholesky_adjoint.argtypes = [i64, vp_, i64, vp_, i64, vp_, i64]
         lib.oracle_multiply.restype = C.c_int
         lib.oracle_multiply.argtypes = [C.POINTER(_abi.MultiplyArgs)]
         lib.oracle_density_eval.restype = C.c_int
@@ -86,6 +91,11 @@ def ref_lib():
             lib.stanref_multiply.argtypes = [l, l, l, dp, dp, dp, dp, C.c_char_p, i]
             lib.stanref_multiply_rev.restype = i
             lib.stanref_multiply_rev.argtypes = [l, l, l, dp, dp, dp, i, dp, dp, dp, dp, C.c_char_p, i]
+        if hasattr(lib, "stanref_cholesky"):
+            lib.stanref_cholesky.restype = i
+            lib.stanref_cholesky.argtypes = [l, dp, dp, dp, C.c_char_p, i]
+            lib.stanref_cholesky_rev.restype = i
+            lib.stanref_cholesky_rev.argtypes = [l, dp, dp, dp, dp, dp, C.c_char_p, i]
         lib.stanref_init_threads.restype = i
         lib.stanref_init_threads.argtypes = [i]
         lib.stanref_shards_create.restype = C.c_void_p
@@ -571,3 +581,47 @@ def ref_multiply_rev(a, b, w, var_mask=3):
         raise RefError(rc, err.value.decode())
     return {"c": c, "da": da if var_mask & 1 else None, "db": db if var_mask & 2 else None,
             "forward_s": float(secs[0]), "grad_s": float(secs[1])}
+
+
+# ------------------------------------------------------------------------------------------
+# Cholesky factor and its reverse-mode adjoint
+def oracle_cholesky(a):
+    """(rc, L): lower factor by the plain-C column algorithm; rc = NOT_POS_DEF where the reference throws."""
+    a = _fmat(a)
+    n = a.shape[0]
+    l = np.zeros((n, n), order="F")
+    rc = oracle_lib().oracle_cholesky_decompose(n, a.ctypes.data, max(n, 1), l.ctypes.data, max(n, 1))
+    return rc, l
+
+
+def oracle_cholesky_adjoint(l, l_adj):
+    """adjoint of the lower triangle of A given L and the adjoint of its lower triangle (unblocked loops)."""
+    l, l_adj = _fmat(l), _fmat(l_adj)
+    n = l.shape[0]
+    out = np.zeros((n, n), order="F")
+    rc = oracle_lib().oracle_cholesky_adjoint(n, l.ctypes.data, max(n, 1), l_adj.ctypes.data, max(n, 1), out.ctypes.data, max(n, 1))
+    assert rc == 0
+    return out
+
+
+def ref_cholesky(a):
+    a = _fmat(a)
+    n = a.shape[0]
+    l, secs = np.zeros((n, n), order="F"), np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_cholesky(n, a.ctypes.data, l.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return l, float(secs[0])
+
+
+def ref_cholesky_rev(a, w):
+    """L = cholesky_decompose(A_v), f = sum(tril(W) * L): returns L, dA (lower triangle) and the two timings."""
+    a, w = _fmat(a), _fmat(w)
+    n = a.shape[0]
+    l, a_adj, secs = np.zeros((n, n), order="F"), np.zeros((n, n), order="F"), np.zeros(2)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_cholesky_rev(n, a.ctypes.data, w.ctypes.data, l.ctypes.data, a_adj.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return {"l": l, "a_adj": a_adj, "forward_s": float(secs[0]), "grad_s": float(secs[1])}

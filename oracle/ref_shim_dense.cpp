@@ -97,4 +97,57 @@ int stanref_multiply_rev(long m, long n, long k, const double* a, const double* 
       err, errlen);
 }
 
+// L = cholesky_decompose(A) for a double matrix (prim/mat/fun/cholesky_decompose.hpp:34-62); rc 1 when the
+// reference throws std::domain_error (not symmetric / not positive definite)
+int stanref_cholesky(long n, const double* a, double* l, double* seconds, char* err, int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d A = Eigen::Map<const matrix_d>(a, n, n);
+        auto t0 = std::chrono::steady_clock::now();
+        matrix_d L = stan::math::cholesky_decompose(A);
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        Eigen::Map<matrix_d>(l, n, n) = L;
+      },
+      err, errlen);
+}
+
+// Reverse mode: L = cholesky_decompose(A_v) (rev/mat/fun/cholesky_decompose.hpp:396-440: cholesky_scalar up to
+// n = 35, cholesky_block above), f = sum_ij W_ij L_ij over the lower triangle, a_adj = df/dA for the lower triangle
+// of A (the operands of the vari; zeros above).  seconds[0]: forward, seconds[1]: grad().
+int stanref_cholesky_rev(long n, const double* a, const double* w, double* l, double* a_adj, double* seconds, char* err,
+                         int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d A = Eigen::Map<const matrix_d>(a, n, n);
+        matrix_v Av = to_var(A);
+        auto t0 = std::chrono::steady_clock::now();
+        matrix_v Lv = stan::math::cholesky_decompose(Av);
+        auto t1 = std::chrono::steady_clock::now();
+        std::vector<var> ops;
+        std::vector<double> grads;
+        double val = 0;
+        for (long j = 0; j < n; ++j)
+          for (long i = j; i < n; ++i) {
+            ops.push_back(Lv(i, j));
+            grads.push_back(w[j * n + i]);
+            val += w[j * n + i] * Lv(i, j).val();
+          }
+        var f = stan::math::precomputed_gradients(val, ops, grads);
+        auto t2 = std::chrono::steady_clock::now();
+        f.grad();
+        auto t3 = std::chrono::steady_clock::now();
+        if (seconds) {
+          seconds[0] = std::chrono::duration<double>(t1 - t0).count();
+          seconds[1] = std::chrono::duration<double>(t3 - t2).count();
+        }
+        for (long j = 0; j < n; ++j)
+          for (long i = 0; i < n; ++i) {
+            l[j * n + i] = i >= j ? Lv(i, j).val() : 0.0;
+            a_adj[j * n + i] = i >= j ? Av(i, j).adj() : 0.0;
+          }
+      },
+      err, errlen);
+}
+
 }  // extern "C"

@@ -17,6 +17,11 @@
 #include <stan/math/cuda/categorical_logit_glm_lpmf.hpp>
 #include <stan/math/cuda/normal_lpdf.hpp>
 #include <stan/math/cuda/student_t_lpdf.hpp>
+#include <stan/math/cuda/matrix_cuda.hpp>
+#include <stan/math/cuda/multiply.hpp>
+#include <stan/math/cuda/rev_multiply.hpp>
+#include <stan/math/cuda/cholesky_decompose.hpp>
+#include <stan/math/cuda/rev_cholesky_decompose.hpp>
 #include <stan/math/cuda/map_rect_devices.hpp>
 #endif
 #endif

@@ -48,6 +48,36 @@ add("cancelling", a - a @ b @ b.T, b)
 # wide dynamic range
 add("wide_range", rng.standard_normal((30, 50)) * 10.0 ** rng.uniform(-8, 8, (30, 50)), rng.standard_normal((50, 20)))
 
+# ---- cholesky_decompose: factor and reverse sweep (rev/mat/fun/cholesky_decompose.hpp: cholesky_scalar up to n = 35,
+# cholesky_block above) for f = sum(tril(W) * L)
+chol_names = []
+
+
+def add_chol(name, a, w=None):
+    a = np.asarray(a, float)
+    n = a.shape[0]
+    rng = np.random.default_rng(1000 + len(chol_names))
+    w = np.tril(rng.uniform(-1, 1, (n, n))) if w is None else np.tril(np.asarray(w, float))
+    p = "chol/%s/" % name
+    l, _ = L.ref_cholesky(a)
+    r = L.ref_cholesky_rev(a, w)
+    assert np.array_equal(np.tril(r["l"]), np.tril(l))
+    out[p + "a"], out[p + "w"], out[p + "l"], out[p + "a_adj"] = a, w, l, r["a_adj"]
+    chol_names.append(name)
+
+
+# test/unit/math/opencl/cholesky_decompose_test.cpp:13-17 (the 3 x 3 factor is [[5,0,0],[3,3,0],[-1,1,3]])
+add_chol("fixture_3x3", [[25, 15, -5], [15, 18, 0], [-5, 0, 11]])
+add_chol("fixture_4x4", [[18, 22, 54, 42], [22, 70, 86, 62], [54, 86, 174, 134], [42, 62, 134, 106]])
+for n in (1, 2, 10, 35, 36, 64, 65, 100):
+    x = rng.uniform(-1, 1, (n, n))
+    a = x @ x.T + n * np.eye(n)
+    add_chol("spd_%d" % n, 0.5 * (a + a.T))
+# a GP covariance with small jitter: condition number ~1e6
+t = np.linspace(0, 3, 60)
+add_chol("gp_60", 0.75 ** 2 * np.exp(-0.5 * (t[:, None] - t[None, :]) ** 2 / 0.5 ** 2) + 1e-4 * np.eye(60))
+out["chol_cases"] = np.array(chol_names)
+
 out["cases"] = np.array(names)
 np.savez_compressed(os.path.join(ROOT, "tests", "golden", "dense_golden.npz"), **out)
-print("wrote %d cases" % len(names))
+print("wrote %d multiply cases, %d cholesky cases" % (len(names), len(chol_names)))

@@ -27,6 +27,8 @@ int oracle_glm_eval(const stan_cuda_glm_args* a);
 int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a);
 int oracle_student_t_lpdf_eval(const stan_cuda_student_t_args* a);
 int oracle_multiply(const stan_cuda_multiply_args* g);
+int oracle_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl);
+int oracle_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda);
 int oracle_density_eval(const stan_cuda_density_args* a);
 
 static __thread char tl_error[256];
@@ -236,6 +238,18 @@ int stan_cuda_multiply(const stan_cuda_multiply_args* g) {
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
   TIMED(oracle_multiply(g));
   return rc < 0 ? fail(rc, "stan_cuda_multiply: bad argument") : rc;
+}
+
+int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {
+  if (n < 0 || (n > 0 && (!a || !l || lda < n || ldl < n))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_cholesky_decompose: bad argument");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  return oracle_cholesky_decompose(n, a, lda, l, ldl);
+}
+
+int stan_cuda_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda) {
+  if (n < 0 || (n > 0 && (!l || !l_adj || !a_adj))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_cholesky_adjoint: bad argument");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  return oracle_cholesky_adjoint(n, l, ldl, l_adj, ldadj, a_adj, lda);
 }
 
 /* the product returns pinned memory of the calling thread; pageable memory serves a host-only run */

@@ -67,6 +67,44 @@ def test_oracle_matches_compiled_reference_on_fresh_inputs():
         assert product_error(L.oracle_multiply(a, w, trans_a=True), ref["db"], a.T, w) <= 1e-13
 
 
+def _chol_case(g, name):
+    p = "chol/%s/" % name
+    return {k: g[p + k] for k in ("a", "w", "l", "a_adj")}
+
+
+def lower_rel_err(got, ref):
+    """the reference's own metric for its OpenCL factor (test/unit/math/opencl/cholesky_decompose_test.cpp:52-60):
+    worst relative error over the lower triangle, with the parity gate's floor of 1e-6 * max|ref|"""
+    got, ref = np.tril(np.asarray(got)), np.tril(np.asarray(ref))
+    if ref.size == 0:
+        return 0.0
+    scale = np.maximum(np.abs(ref), 1e-6 * np.max(np.abs(ref)))
+    scale = np.where(scale == 0, 1.0, scale)
+    return float(np.max(np.abs(got - ref) / scale))
+
+
+def test_oracle_cholesky_matches_golden(golden_mm):
+    assert len(golden_mm["chol_cases"]) >= 10
+    for name in golden_mm["chol_cases"]:
+        c = _chol_case(golden_mm, str(name))
+        rc, l = L.oracle_cholesky(c["a"])
+        # the GP case has condition number ~1e6: two backward-stable algorithms agree to cond * eps, not to eps
+        tol = 1e-9 if str(name).startswith("gp") else 1e-12
+        assert rc == 0 and lower_rel_err(l, c["l"]) <= tol, name
+        assert not np.triu(l, 1).any()
+        assert lower_rel_err(L.oracle_cholesky_adjoint(c["l"], c["w"]), c["a_adj"]) <= tol, name
+    fx = _chol_case(golden_mm, "fixture_3x3")
+    assert np.allclose(fx["l"], [[5, 0, 0], [3, 3, 0], [-1, 1, 3]], atol=1e-14)
+
+
+def test_oracle_cholesky_rejects_what_the_reference_rejects():
+    for bad in (-np.eye(3), np.array([[1.0, 2.0], [2.0, 1.0]]), np.array([[1.0, np.nan], [np.nan, 1.0]]), np.zeros((2, 2))):
+        assert L.oracle_cholesky(bad)[0] == _abi.NOT_POS_DEF
+        if L.have_ref():
+            with pytest.raises(L.RefError):
+                L.ref_cholesky(bad)
+
+
 # ------------------------------------------------------------------------------------------ GPU
 @pytest.fixture(scope="module")
 def dense():
@@ -169,3 +207,73 @@ def test_full_size_properties(dense):
     c2 = (da @ dense.MatrixCuda(b2)).to_host()
     csum = (da @ dense.MatrixCuda(b + b2)).to_host()
     assert product_error(csum, c + c2, a, np.abs(b) + np.abs(b2)) <= 1e-10
+
+
+# ---- cholesky_decompose ------------------------------------------------------------------------------------
+def _spd(n, seed):
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(-1, 1, (n, n))
+    a = x @ x.T + n * np.eye(n)
+    return 0.5 * (a + a.T)
+
+
+@pytest.mark.gpu
+def test_device_cholesky_matches_golden(dense, golden_mm):
+    for name in golden_mm["chol_cases"]:
+        c = _chol_case(golden_mm, str(name))
+        l = dense.cholesky_decompose(c["a"])
+        tol = 1e-8 if str(name).startswith("gp") else 1e-10   # cond(A) ~ 1e6 for the GP case
+        assert lower_rel_err(l, c["l"]) <= tol, name
+        assert not np.triu(l, 1).any()
+        assert lower_rel_err(dense.cholesky_adjoint(c["l"], c["w"]), c["a_adj"]) <= tol, name
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 2, 3, 31, 63, 64, 65, 127, 128, 129, 200, 321, 640, 1000])
+def test_device_cholesky_matches_oracle(dense, n):
+    a = _spd(n, n)
+    rc, ref = L.oracle_cholesky(a)
+    assert rc == 0
+    l = dense.cholesky_decompose(a)
+    assert lower_rel_err(l, ref) <= 1e-10
+    w = np.tril(np.random.default_rng(n + 1).uniform(-1, 1, (n, n)))
+    if n <= 400:   # the oracle's unblocked sweep is O(n^3) scalar loops
+        assert lower_rel_err(dense.cholesky_adjoint(ref, w), L.oracle_cholesky_adjoint(ref, w)) <= 1e-10
+
+
+@pytest.mark.gpu
+def test_device_cholesky_rejects_what_the_reference_rejects(dense):
+    for bad in (-np.eye(3), np.array([[1.0, 2.0], [2.0, 1.0]]), np.array([[1.0, np.nan], [np.nan, 1.0]]), np.zeros((2, 2))):
+        with pytest.raises(dense.NotPositiveDefinite):
+            dense.cholesky_decompose(bad)
+    big = _spd(300, 7)
+    big[250, 250] = -1.0    # fails in the fourth block: the flag survives the remaining steps
+    with pytest.raises(dense.NotPositiveDefinite):
+        dense.cholesky_decompose(big)
+    with pytest.raises(ValueError, match="square"):
+        dense.cholesky_decompose(np.zeros((2, 3)))
+    assert dense.cholesky_decompose(np.zeros((0, 0))).shape == (0, 0)
+
+
+@pytest.mark.gpu
+def test_cholesky_full_size_properties(dense):
+    """n = 4096: L L' reproduces A to the backward-error bound, L is lower triangular with a positive diagonal, the
+    factor of a block-diagonal matrix is block diagonal, and the reverse sweep satisfies the identity
+    <L_adj, dL> = <A_adj, dA> for a random symmetric perturbation (directional derivative by finite differences)."""
+    n = 4096
+    a = _spd(n, 5)
+    l = dense.cholesky_decompose(a)
+    assert not np.triu(l, 1).any() and np.all(np.diag(l) > 0)
+    resid = dense.multiply_host(l, l, trans_b=True) - a
+    assert np.max(np.abs(resid)) <= 1e-12 * np.max(np.abs(a)) * n ** 0.5
+    rng = np.random.default_rng(6)
+    w = np.tril(rng.uniform(-1, 1, (n, n)))
+    a_adj = dense.cholesky_adjoint(l, w)
+    e = rng.uniform(-1, 1, (n, n))
+    e = 0.5 * (e + e.T)
+    h = 1e-6
+    lp, lm = dense.cholesky_decompose(a + h * e), dense.cholesky_decompose(a - h * e)
+    fd = np.sum(w * (lp - lm)) / (2 * h)
+    # the operands are the lower triangle of A only: a symmetric perturbation moves (i, j) and (j, i) together
+    analytic = np.sum(a_adj * np.tril(e))
+    assert abs(fd - analytic) <= 1e-6 * max(abs(analytic), 1.0)
