@@ -336,8 +336,15 @@ STAN_CUDA_API int stan_cuda_multiply(const stan_cuda_multiply_args* a);
  *   STAN_CUDA_NOT_POS_DEF when a pivot is not positive -- the wrapper then runs the reference's LLT +
  *   check_pos_definite on the host to throw the identical exception.
  * adjoint: given l and the adjoints l_adj of its lower triangle, writes the adjoints of the lower triangle of a into
- *   a_adj (n x n; the strict upper triangle of a_adj is not meaningful). */
+ *   a_adj (n x n, zeros above the diagonal: only the lower triangle of a is an operand of the reference's node). */
 STAN_CUDA_API int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl);
+/* Triangular solve x (n x m) = op(A)^-1 b (the mdivide_left_tri hooks of
+ * stan/math/prim/mat/fun/mdivide_left_tri.hpp:58-100 and stan/math/rev/mat/fun/mdivide_left_tri.hpp:69-82, 91-105,
+ * 145-159, 170-183, for which the OpenCL backend has tri_inverse + multiply, stan/math/opencl/tri_inverse.hpp).
+ * A is n x n, triangular: lower != 0 reads its lower triangle, else its upper; op(A) = A' when trans != 0 (the
+ * reverse sweep's A^-T adj).  Host matrices, column-major; x may be b. */
+STAN_CUDA_API int stan_cuda_tri_solve(int lower, int trans, int64_t n, int64_t m, const double* a, int64_t lda, const double* b,
+                                      int64_t ldb, double* x, int64_t ldx);
 STAN_CUDA_API int stan_cuda_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj,
                                              double* a_adj, int64_t lda);
 /* Page-locked staging memory of the calling thread (at least `bytes`, valid until the thread's next

@@ -13,7 +13,7 @@
 //   3. dgemm (N, T), lower-only     A[j+64:, j+64:] -= panel * panel'
 // Reverse, blocks from the bottom up (the block boundaries are multiples of 64 from the top: any blocking is valid
 // and this one keeps every sub-block 16-byte aligned):
-//   W = D^-1 (tri_inv_kernel);  Cb = Cb W;  Bb -= Cb R;  Db -= Cb' C;  Db = sym(D, W, Db) (symbolic_rev_kernel);
+//   W_b = D_b^-1 for all blocks (tri_inv_blocks_kernel, one launch);  Cb = Cb W;  Bb -= Cb R;  Db -= Cb' C;  Db = sym(D, W, Db) (symbolic_rev_kernel);
 //   Rb -= Cb' B + Db_sym R;  diag(Db) *= 1/2.
 // The products are the DMMA kernel of gemm.cu on sub-blocks; the three small kernels run one CTA each and are the
 // serial spine of both sweeps (n / 64 steps).
@@ -100,15 +100,30 @@ __global__ void __launch_bounds__(kThreads) potrf_inv_kernel(const double* __res
   for (int idx = tid; idx < kNB * kNB; idx += kThreads) W[idx] = at(Wm, idx % kNB, idx / kNB);  // column-major, ld = 64
 }
 
-// W = D^-1 for a lower-triangular diagonal block of L (reverse sweep)
-__global__ void __launch_bounds__(kThreads) tri_inv_kernel(const double* __restrict__ Dg, int64_t ld, int jb, double* __restrict__ W) {
+// W_b = D_b^-1 for every 64 x 64 diagonal block D_b of a triangular n x n matrix, one CTA per block (the blocks are
+// independent: one launch instead of one per step of a sweep).  lower: D_b is the lower triangle of the block.
+// Otherwise the block is upper triangular, it is loaded transposed, and W_b = (U_b')^-1 = (U_b^-1)': the callers
+// flip the transpose flag of the product that applies it.
+__global__ void __launch_bounds__(kThreads) tri_inv_blocks_kernel(const double* __restrict__ A, int64_t ld, int64_t n, int lower,
+                                                                 double* __restrict__ Wall) {
   extern __shared__ double sm[];
   double* D = sm;
   double* Wm = sm + kNB * kLD;
   const int tid = threadIdx.x;
-  load_lower(D, Dg, ld, jb, tid);
+  const int64_t j = int64_t(blockIdx.x) * kNB;
+  const int jb = int(min(int64_t(kNB), n - j));
+  const double* Dg = A + j + j * ld;
+  if (lower) {
+    load_lower(D, Dg, ld, jb, tid);
+  } else {
+    for (int idx = tid; idx < kNB * kNB; idx += kThreads) {
+      const int r = idx / kNB, c = idx % kNB;  // element (r, c) of the transposed block = U(c, r), kept for r >= c
+      at(D, r, c) = (r < jb && c <= r) ? Dg[int64_t(r) * ld + c] : 0.0;
+    }
+  }
   __syncthreads();
   tri_inverse_shared(D, Wm, jb, tid);
+  double* W = Wall + int64_t(blockIdx.x) * kNB * kNB;
   for (int idx = tid; idx < kNB * kNB; idx += kThreads) W[idx] = at(Wm, idx % kNB, idx / kNB);
 }
 
@@ -168,6 +183,14 @@ __global__ void __launch_bounds__(kThreads) symbolic_rev_kernel(const double* __
   }
 }
 
+// zero the strict upper triangle of an n x n matrix
+__global__ void zero_strict_upper_kernel(double* __restrict__ L, int64_t ld, int64_t n) {
+  const int64_t r = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, c = blockIdx.y * int64_t(64);
+  if (r >= n) return;
+  for (int64_t cc = c; cc < min(n, c + 64); ++cc)
+    if (r < cc) L[cc * ld + r] = 0.0;
+}
+
 struct DeviceBuf {
   double* p = nullptr;
   cudaStream_t stream = nullptr;
@@ -186,7 +209,7 @@ int64_t padded(int64_t n) { return n <= 0 ? 16 : (n + 15) / 16 * 16; }
 int set_smem_limits() {  // per device (the attribute belongs to the function on the current device): cheap, every call
   SC_CUDA(cudaFuncSetAttribute(symbolic_rev_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(4 * kNB * kLD * sizeof(double))));
   SC_CUDA(cudaFuncSetAttribute(potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(2 * kNB * kLD * sizeof(double))));
-  SC_CUDA(cudaFuncSetAttribute(tri_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(2 * kNB * kLD * sizeof(double))));
+  SC_CUDA(cudaFuncSetAttribute(tri_inv_blocks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(2 * kNB * kLD * sizeof(double))));
   return STAN_CUDA_OK;
 }
 
@@ -262,39 +285,98 @@ int cholesky_adjoint_host(int64_t n, const double* l, int64_t ldl, const double*
   DeviceBuf L, Lb, W, Dsym, Tmp;
   SC_TRY(L.alloc(size_t(ld) * n, s));
   SC_TRY(Lb.alloc(size_t(ld) * n, s));
-  SC_TRY(W.alloc(kNB * kNB, s));
+  const int64_t nblk = (n + kNB - 1) / kNB;
+  SC_TRY(W.alloc(size_t(nblk) * kNB * kNB, s));
   SC_TRY(Dsym.alloc(kNB * kNB, s));
   SC_TRY(Tmp.alloc(size_t(ld) * kNB, s));
   SC_TRY(dense_copy_to_device(L.p, ld, l, ldl, n, n, s));
   SC_TRY(dense_copy_to_device(Lb.p, ld, l_adj, ldadj, n, n, s));
   counters().bytes_uploaded.fetch_add(2 * uint64_t(n) * uint64_t(n) * sizeof(double));
   const size_t smem2 = 2 * kNB * kLD * sizeof(double), smem4 = 4 * kNB * kLD * sizeof(double);
-  const int64_t nblk = (n + kNB - 1) / kNB;
+  tri_inv_blocks_kernel<<<unsigned(nblk), kThreads, smem2, s>>>(L.p, ld, n, 1, W.p);  // D_b^-1 for every diagonal block
+  SC_CUDA(cudaGetLastError());
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
   for (int64_t b = nblk - 1; b >= 0; --b) {
     const int64_t j = b * kNB, k = std::min<int64_t>(n, j + kNB);
     const int kj = int(k - j);
     const int64_t mk = n - k;
     double *D = L.p + j + j * ld, *R = L.p + j, *B = L.p + k, *C = L.p + k + j * ld;
     double *Db = Lb.p + j + j * ld, *Rb = Lb.p + j, *Bb = Lb.p + k, *Cb = Lb.p + k + j * ld;
-    tri_inv_kernel<<<1, kThreads, smem2, s>>>(D, ld, kj, W.p);
-    SC_CUDA(cudaGetLastError());
+    const double* Wb = W.p + b * kNB * kNB;
     if (mk > 0) {
       // Cb = Cb D^-1                                                         (:147-151 / :358)
-      SC_TRY(dgemm(dev, false, false, false, mk, kj, kj, 1.0, Cb, ld, W.p, kNB, 0.0, Tmp.p, ld, s));
+      SC_TRY(dgemm(dev, false, false, false, mk, kj, kj, 1.0, Cb, ld, Wb, kNB, 0.0, Tmp.p, ld, s));
       SC_CUDA(cudaMemcpy2DAsync(Cb, size_t(ld) * sizeof(double), Tmp.p, size_t(ld) * sizeof(double), size_t(mk) * sizeof(double),
                                 size_t(kj), cudaMemcpyDeviceToDevice, s));
       if (j > 0) SC_TRY(dgemm(dev, false, false, false, mk, j, kj, -1.0, Cb, ld, R, ld, 1.0, Bb, ld, s));  // Bb -= Cb R   (:152 / :359)
       SC_TRY(dgemm(dev, true, false, false, kj, kj, mk, -1.0, Cb, ld, C, ld, 1.0, Db, ld, s));            // Db -= Cb' C  (:153 / :360)
     }
-    symbolic_rev_kernel<<<1, kThreads, smem4, s>>>(D, ld, W.p, Db, ld, kj, Dsym.p);                         // :155 / :362
+    symbolic_rev_kernel<<<1, kThreads, smem4, s>>>(D, ld, Wb, Db, ld, kj, Dsym.p);                         // :155 / :362
     SC_CUDA(cudaGetLastError());
-    counters().launches.fetch_add(2, std::memory_order_relaxed);
+    counters().launches.fetch_add(1, std::memory_order_relaxed);
     if (j > 0) {
       if (mk > 0) SC_TRY(dgemm(dev, true, false, false, kj, j, mk, -1.0, Cb, ld, B, ld, 1.0, Rb, ld, s));  // Rb -= Cb' B   (:156 / :364)
       SC_TRY(dgemm(dev, false, false, false, kj, j, kj, -1.0, Dsym.p, kNB, R, ld, 1.0, Rb, ld, s));        // Rb -= Db_sym R (:157 / :364)
     }
   }
-  SC_TRY(dense_copy_to_host(a_adj, lda, Lb.p, ld, n, n, s));  // the caller reads the lower triangle
+  // the strict upper triangle holds scratch of the symmetric updates: the operands are the lower triangle of A only
+  zero_strict_upper_kernel<<<dim3(unsigned((n + 255) / 256), unsigned((n + 63) / 64)), 256, 0, s>>>(Lb.p, ld, n);
+  SC_CUDA(cudaGetLastError());
+  SC_TRY(dense_copy_to_host(a_adj, lda, Lb.p, ld, n, n, s));
+  counters().evals.fetch_add(1, std::memory_order_relaxed);
+  return STAN_CUDA_OK;
+}
+
+// x (n x m) = op(A)^-1 b for a triangular A (lower != 0: the lower triangle is read, else the upper), op = transpose
+// when trans != 0.  Blocked substitution: all diagonal blocks are inverted in one launch, then for each block row i
+// (top down for lower / no transpose and upper / transpose, bottom up otherwise)
+//   X_i = op(A_ii)^-1 X_i      a 64 x m product with the block inverse
+//   X_r -= op(A)[r, i] X_i     for the rows r still to be solved: one product with inner dimension 64
+// The reference's OpenCL path forms the whole inverse (tri_inverse) and multiplies (prim/mat/fun/mdivide_left_tri.hpp
+// :63-72); substitution does a third of the work and keeps the error at that of the 64 x 64 blocks.
+int tri_solve_host(int lower, int trans, int64_t n, int64_t m, const double* a, int64_t lda, const double* b, int64_t ldb, double* x,
+                   int64_t ldx) {
+  NvtxRange range("stan_cuda_tri_solve");
+  if (n < 0 || m < 0 || (n > 0 && (!a || lda < n)) || (n > 0 && m > 0 && (!b || !x || ldb < n || ldx < n)))
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_tri_solve: bad argument");
+  if (n == 0 || m == 0) return STAN_CUDA_OK;
+  SC_TRY(ensure_init());
+  SC_TRY(set_smem_limits());
+  const int dev = scope_device_ordinal();
+  ThreadDev* td;
+  SC_TRY(thread_dev(dev, &td));
+  SC_CUDA(cudaSetDevice(dev));
+  cudaStream_t s = td->stream;
+  const int64_t ld = padded(n), nblk = (n + kNB - 1) / kNB;
+  DeviceBuf A, X, W, Tmp;
+  SC_TRY(A.alloc(size_t(ld) * n, s));
+  SC_TRY(X.alloc(size_t(ld) * m, s));
+  SC_TRY(W.alloc(size_t(nblk) * kNB * kNB, s));
+  SC_TRY(Tmp.alloc(size_t(kNB) * m, s));
+  SC_TRY(dense_copy_to_device(A.p, ld, a, lda, n, n, s));
+  SC_TRY(dense_copy_to_device(X.p, ld, b, ldb, n, m, s));
+  counters().bytes_uploaded.fetch_add((uint64_t(n) * uint64_t(n) + uint64_t(n) * uint64_t(m)) * sizeof(double));
+  tri_inv_blocks_kernel<<<unsigned(nblk), kThreads, 2 * kNB * kLD * sizeof(double), s>>>(A.p, ld, n, lower, W.p);
+  SC_CUDA(cudaGetLastError());
+  counters().launches.fetch_add(1, std::memory_order_relaxed);
+  const bool top_down = (lower != 0) != (trans != 0);
+  const bool trans_w = lower ? trans != 0 : trans == 0;  // W_b of an upper block is the transpose of its inverse
+  for (int64_t step = 0; step < nblk; ++step) {
+    const int64_t bi = top_down ? step : nblk - 1 - step;
+    const int64_t i0 = bi * kNB, ib = std::min<int64_t>(kNB, n - i0);
+    double* Xi = X.p + i0;
+    SC_TRY(dgemm(dev, trans_w, false, false, ib, m, ib, 1.0, W.p + bi * kNB * kNB, kNB, Xi, ld, 0.0, Tmp.p, kNB, s));
+    SC_CUDA(cudaMemcpy2DAsync(Xi, size_t(ld) * sizeof(double), Tmp.p, size_t(kNB) * sizeof(double), size_t(ib) * sizeof(double),
+                              size_t(m), cudaMemcpyDeviceToDevice, s));
+    // rows still to be solved and the block of op(A) that couples them to block row i
+    const int64_t r0 = top_down ? i0 + ib : 0, nr = top_down ? n - i0 - ib : i0;
+    if (nr > 0) {
+      // not transposed: A[r, i] (rows r0.., columns i0..);  transposed: A[i, r]' (rows i0.., columns r0..)
+      const double* Ari = trans ? A.p + i0 + r0 * ld : A.p + r0 + i0 * ld;
+      SC_TRY(dgemm(dev, trans != 0, false, false, nr, m, ib, -1.0, Ari, ld, Tmp.p, kNB, 1.0, X.p + r0, ld, s));
+    }
+  }
+  SC_TRY(dense_copy_to_host(x, ldx, X.p, ld, n, m, s));
   counters().evals.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
 }
@@ -307,5 +389,9 @@ int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double
 }
 int stan_cuda_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda) {
   return stancuda::cholesky_adjoint_host(n, l, ldl, l_adj, ldadj, a_adj, lda);
+}
+int stan_cuda_tri_solve(int lower, int trans, int64_t n, int64_t m, const double* a, int64_t lda, const double* b, int64_t ldb, double* x,
+                        int64_t ldx) {
+  return stancuda::tri_solve_host(lower, trans, n, m, a, lda, b, ldb, x, ldx);
 }
 }

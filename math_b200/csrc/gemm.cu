@@ -67,7 +67,6 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // LOWER_ONLY skips the tiles strictly above the diagonal (the symmetric rank-k updates of the Cholesky routines).
 template <int BX, bool DEEP>
 struct OperandTile {
-  static constexpr int kStride = DEEP ? 12 : BX + 4;
   static constexpr int kDoubles = DEEP ? BX * 12 : kBK * (BX + 4);
   static constexpr int kPerThread = BX * kBK / kGemmThreads;  // 2 or 4 contiguous doubles
   static_assert(kPerThread == 2 || kPerThread == 4, "one or two 16-byte loads per thread");
@@ -75,36 +74,46 @@ struct OperandTile {
   __device__ static int x_of(int tid) { return DEEP ? tid / (kBK / kPerThread) : (tid % (BX / kPerThread)) * kPerThread; }
   __device__ static int k_of(int tid) { return DEEP ? (tid % (kBK / kPerThread)) * kPerThread : tid / (BX / kPerThread); }
   __device__ static int offset(int x, int k) { return DEEP ? x * 12 + k : k * (BX + 4) + x; }
-  // global element (x, k) of op(P): P[x + k * ld] when x is contiguous, P[k + x * ld] when k is
-  __device__ static void load(const double* __restrict__ P, int64_t ld, int64_t x0, int64_t X, int64_t k0, int64_t K, int tid,
-                              double* r) {
-    const int64_t x = x0 + x_of(tid), k = k0 + k_of(tid);
-#pragma unroll
-    for (int q = 0; q < kPerThread; ++q) r[q] = 0.0;
-    if (DEEP) {
-      if (x >= X) return;
-      const double* p = P + x * ld + k;
-#pragma unroll
-      for (int q = 0; q < kPerThread; q += 2) {
-        if (k + q < K) {
-          const double2 v = __ldg(reinterpret_cast<const double2*>(p + q));
-          r[q] = v.x;
-          r[q + 1] = (k + q + 1 < K) ? v.y : 0.0;
-        }
-      }
-    } else {
-      if (k >= K) return;
-      const double* p = P + k * ld + x;
-#pragma unroll
-      for (int q = 0; q < kPerThread; q += 2) {
-        if (x + q < X) {
-          const double2 v = __ldg(reinterpret_cast<const double2*>(p + q));
-          r[q] = v.x;
-          r[q + 1] = (x + q + 1 < X) ? v.y : 0.0;
-        }
+  // Per-thread loader of this operand's share of one stage: element (x, k) of op(P) is P[x + k * ld] when x is
+  // contiguous and P[k + x * ld] when k is.  No test along x is ever needed: an element with x >= X only feeds rows
+  // (columns) of C that the epilogue does not store, so such a thread just reads a valid address (x clamped to 0; a
+  // group of 2 or 4 that straddles X stays inside the leading dimension, which is a multiple of 4).  Along k only
+  // the last, partial stage tests, element by element.  The pointer advances by a constant per stage.
+  struct Loader {
+    const double* p;   // this thread's first element at k0 = 0
+    int64_t step;      // pointer increment per stage
+    int kt;            // this thread's k offset inside a stage
+    __device__ Loader(const double* P, int64_t ld, int64_t x0, int64_t X, int tid) {
+      int64_t x = x0 + x_of(tid);
+      if (x >= X) x = 0;
+      kt = k_of(tid);
+      if (DEEP) {
+        p = P + x * ld + kt;
+        step = kBK;
+      } else {
+        p = P + int64_t(kt) * ld + x;
+        step = int64_t(kBK) * ld;
       }
     }
-  }
+    // k_left = K - k0 of the stage being loaded (> 0)
+    __device__ void load(int64_t stage, int64_t k_left, double* r) const {
+      const double* src = p + stage * step;
+      if (k_left >= kBK) {
+#pragma unroll
+        for (int q = 0; q < kPerThread; q += 2) {
+          const double2 v = __ldg(reinterpret_cast<const double2*>(src + q));
+          r[q] = v.x;
+          r[q + 1] = v.y;
+        }
+      } else if (DEEP) {
+#pragma unroll
+        for (int q = 0; q < kPerThread; ++q) r[q] = kt + q < k_left ? __ldg(src + q) : 0.0;
+      } else {
+#pragma unroll
+        for (int q = 0; q < kPerThread; ++q) r[q] = kt < k_left ? __ldg(src + q) : 0.0;
+      }
+    }
+  };
   __device__ static void store(double* T, int tid, const double* r) {
     double* t = T + offset(x_of(tid), k_of(tid));
 #pragma unroll
@@ -115,7 +124,16 @@ struct OperandTile {
 template <int BM, int BN, int WARPS_M, int MIN_CTAS, bool TA, bool TB, bool LOWER_ONLY>
 __global__ void __launch_bounds__(kGemmThreads, MIN_CTAS)
 dgemm_kernel(int64_t M, int64_t N, int64_t K, double alpha, const double* __restrict__ A, int64_t lda, const double* __restrict__ B,
-             int64_t ldb, double beta, double* __restrict__ C, int64_t ldc) {
+             int64_t ldb, double beta, double* __restrict__ C, int64_t ldc, int64_t k_chunk, int64_t c_split_stride) {
+  // split-K (gridDim.z > 1): slice z covers k in [z * k_chunk, min(K, (z + 1) * k_chunk)) and writes its partial
+  // product (alpha = 1, beta = 0 from the launcher) into its own copy of C, c_split_stride doubles further on
+  if (gridDim.z > 1) {
+    const int64_t k_begin = int64_t(blockIdx.z) * k_chunk;
+    A += TA ? k_begin : k_begin * lda;
+    B += TB ? k_begin * ldb : k_begin;
+    C += int64_t(blockIdx.z) * c_split_stride;
+    K = min(K - k_begin, k_chunk);
+  }
   constexpr int WARPS_N = kGemmThreads / 32 / WARPS_M;
   constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;  // warp tile
   constexpr int TM = WM / 8, TN = WN / 8;              // DMMA fragments per warp tile
@@ -138,16 +156,18 @@ dgemm_kernel(int64_t M, int64_t N, int64_t K, double alpha, const double* __rest
 
   double ra[TileA::kPerThread], rb[TileB::kPerThread];
   const int64_t steps = (K + kBK - 1) / kBK;
-  TileA::load(A, lda, m0, M, 0, K, tid, ra);
-  TileB::load(B, ldb, n0, N, 0, K, tid, rb);
+  const typename TileA::Loader load_a(A, lda, m0, M, tid);
+  const typename TileB::Loader load_b(B, ldb, n0, N, tid);
+  load_a.load(0, K, ra);
+  load_b.load(0, K, rb);
   TileA::store(As[0], tid, ra);
   TileB::store(Bs[0], tid, rb);
   __syncthreads();
   for (int64_t t = 0; t < steps; ++t) {
     const int buf = int(t & 1);
     if (t + 1 < steps) {
-      TileA::load(A, lda, m0, M, (t + 1) * kBK, K, tid, ra);
-      TileB::load(B, ldb, n0, N, (t + 1) * kBK, K, tid, rb);
+      load_a.load(t + 1, K - (t + 1) * kBK, ra);
+      load_b.load(t + 1, K - (t + 1) * kBK, rb);
     }
 #pragma unroll
     for (int ks = 0; ks < kBK; ks += 4) {
@@ -190,14 +210,29 @@ dgemm_kernel(int64_t M, int64_t N, int64_t K, double alpha, const double* __rest
 
 template <int BM, int BN, int WARPS_M, int MIN_CTAS, bool TA, bool TB, bool LOWER_ONLY>
 int launch_dgemm(int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda, const double* B, int64_t ldb,
-                 double beta, double* C, int64_t ldc, cudaStream_t stream) {
+                 double beta, double* C, int64_t ldc, cudaStream_t stream, int splits = 1, int64_t k_chunk = 0,
+                 int64_t c_split_stride = 0) {
   const int64_t gx = (M + BM - 1) / BM, gy = (N + BN - 1) / BN;
   if (gy > 65535) return fail(STAN_CUDA_ERR_ARG, "dgemm: more than 65535 column tiles");
   dgemm_kernel<BM, BN, WARPS_M, MIN_CTAS, TA, TB, LOWER_ONLY>
-      <<<dim3(unsigned(gx), unsigned(gy)), kGemmThreads, 0, stream>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+      <<<dim3(unsigned(gx), unsigned(gy), unsigned(splits)), kGemmThreads, 0, stream>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc,
+                                                                                        k_chunk, c_split_stride);
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
+}
+
+// C = alpha * (sum of the split-K partials, in slice order) + beta * C
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const double* __restrict__ part, int splits, int64_t stride, int64_t M,
+                                                            int64_t N, int64_t ldp, double alpha, double beta, double* __restrict__ C,
+                                                            int64_t ldc) {
+  const int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (idx >= M * N) return;
+  const int64_t m = idx % M, n = idx / M;
+  double s = 0.0;
+  for (int z = 0; z < splits; ++z) s += part[z * stride + n * ldp + m];
+  double* c = C + n * ldc + m;
+  *c = beta == 0.0 ? alpha * s : fma(alpha, s, beta * *c);
 }
 
 // Tile variants.  0: 128 x 128, warps 2 x 4 (64 x 32 each), one CTA per SM.  1: 128 x 64, warps 4 x 2 (32 x 32 each),
@@ -216,25 +251,50 @@ template <bool TA, bool TB, bool LOWER_ONLY>
 int dgemm_variant(int device, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda, const double* B,
                   int64_t ldb, double beta, double* C, int64_t ldc, cudaStream_t stream) {
   int variant = gemm_tile_override();
+  const int sms = sm_count(device);
   if (variant < 0 || variant > 2) {
     const int64_t tiles = ((M + 127) / 128) * ((N + 63) / 64);
-    variant = tiles >= 2 * int64_t(sm_count(device)) * (LOWER_ONLY ? 2 : 1) ? 1 : 2;
+    variant = tiles >= 2 * int64_t(sms) * (LOWER_ONLY ? 2 : 1) ? 1 : 2;
   }
   if (variant == 0) return launch_dgemm<128, 128, 2, 1, TA, TB, LOWER_ONLY>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream);
   if (variant == 1) return launch_dgemm<128, 64, 4, 2, TA, TB, LOWER_ONLY>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream);
+  // Few tiles and a long K (the A' B products of the Cholesky reverse sweep: a 64 x j result summed over thousands
+  // of rows): split K over blockIdx.z so that the machine is filled, partial products into a workspace, then a
+  // reduction in slice order -- the result does not depend on which SM ran which slice.
+  const int64_t tiles64 = ((M + 63) / 64) * ((N + 63) / 64);
+  if (!LOWER_ONLY && K >= 1024 && tiles64 * 2 <= sms) {
+    int splits = int(std::min<int64_t>(std::min<int64_t>(32, K / 256), (2 * int64_t(sms) + tiles64 - 1) / tiles64));
+    if (splits > 1) {
+      const int64_t k_chunk = ((K + splits - 1) / splits + kBK - 1) / kBK * kBK;
+      splits = int((K + k_chunk - 1) / k_chunk);
+      const int64_t ldp = (M + 3) / 4 * 4, stride = ldp * N;
+      double* part = nullptr;
+      SC_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&part), size_t(stride) * splits * sizeof(double), stream));
+      int rc = launch_dgemm<64, 64, 2, 2, TA, TB, false>(M, N, K, 1.0, A, lda, B, ldb, 0.0, part, ldp, stream, splits, k_chunk, stride);
+      if (rc >= 0) {
+        splitk_reduce_kernel<<<unsigned((M * N + 255) / 256), 256, 0, stream>>>(part, splits, stride, M, N, ldp, alpha, beta, C, ldc);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) rc = fail_cuda(e, "splitk_reduce_kernel", __FILE__, __LINE__);
+        counters().launches.fetch_add(1, std::memory_order_relaxed);
+      }
+      cudaFreeAsync(part, stream);
+      return rc;
+    }
+  }
   return launch_dgemm<64, 64, 2, 2, TA, TB, LOWER_ONLY>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream);
 }
 
 }  // namespace
 
 // C (M x N) = alpha * op(A) * op(B) + beta * C on raw device pointers (sub-blocks of larger matrices included): every
-// pointer 16-byte aligned, every leading dimension even.  With lower_only only the elements with n <= m are
+// operand pointer 32-byte aligned, every operand leading dimension a multiple of 4 (the loads of a tile edge may read
+// up to three elements past the last row of an operand, inside its leading dimension).  With lower_only only the elements with n <= m are
 // computed and written (M == N for the callers: symmetric updates).
 int dgemm(int device, bool trans_a, bool trans_b, bool lower_only, int64_t M, int64_t N, int64_t K, double alpha, const double* A,
           int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc, cudaStream_t stream) {
   if (M <= 0 || N <= 0) return STAN_CUDA_OK;
-  if (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) || (lda & 1) || (ldb & 1))
-    return fail(STAN_CUDA_ERR_ARG, "dgemm: operand not 16-byte aligned");
+  if (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 31) || (lda & 3) || (ldb & 3))
+    return fail(STAN_CUDA_ERR_ARG, "dgemm: operands must be 32-byte aligned with leading dimensions that are multiples of 4");
 #define STAN_CUDA_DGEMM_CASE(TA, TB)                                                                                      \
   if (trans_a == TA && trans_b == TB)                                                                                     \
     return lower_only ? dgemm_variant<TA, TB, true>(device, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, stream)          \

@@ -43,9 +43,12 @@ class MatrixCuda:
         v._h, v._trans, v._owner = self._h, not self._trans, self._owner or self
         return v
 
-    def to_host(self):
+    def to_host(self, out=None):
+        """from_matrix_cl; `out` (optional): an r x c Fortran-ordered array to fill instead of a fresh one"""
         r, c = lib().stan_cuda_matrix_rows(self._h), lib().stan_cuda_matrix_cols(self._h)
-        out = np.zeros((r, c), order="F")
+        if out is None:
+            out = np.zeros((r, c), order="F")
+        assert out.shape == (r, c) and out.flags.f_contiguous and out.dtype == np.float64
         if out.size:
             check(lib().stan_cuda_matrix_download(self._h, out.ctypes.data, max(r, 1)))
         return out.T if self._trans else out
@@ -113,4 +116,22 @@ def cholesky_adjoint(l, l_adj):
     n = l.shape[0]
     out = np.zeros((n, n), order="F")
     check(lib().stan_cuda_cholesky_adjoint(n, l.ctypes.data, max(n, 1), l_adj.ctypes.data, max(n, 1), out.ctypes.data, max(n, 1)))
-    return np.tril(out)
+    return out
+
+
+def tri_solve(a, b, lower=True, trans=False):
+    """op(A)^-1 b for a triangular A (stan_cuda_tri_solve): mdivide_left_tri<Lower | Upper>(A, b) and, with trans, the
+    A^-T adj product of its reverse sweep."""
+    a = _fmat(a)
+    b = np.asarray(b, dtype=np.float64)
+    vec = b.ndim == 1
+    b = _fmat(b.reshape(-1, 1) if vec else b)
+    if a.shape[0] != a.shape[1]:
+        raise ValueError("mdivide_left_tri: Expecting a square matrix; rows of A (%d) and columns of A (%d) must match in size" % a.shape)
+    if a.shape[1] != b.shape[0]:
+        raise ValueError("mdivide_left_tri: Columns of A (%d) and Rows of b (%d) must match in size" % (a.shape[1], b.shape[0]))
+    n, m = a.shape[0], b.shape[1]
+    x = np.zeros((n, m), order="F")
+    check(lib().stan_cuda_tri_solve(int(lower), int(trans), n, m, a.ctypes.data, max(n, 1), b.ctypes.data, max(n, 1),
+                                    x.ctypes.data, max(n, 1)))
+    return x[:, 0] if vec else x

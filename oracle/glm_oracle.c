@@ -491,6 +491,29 @@ int oracle_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const doubl
   return STAN_CUDA_OK;
 }
 
+/* Triangular solve x = op(A)^-1 b by substitution: what Eigen's triangularView<>.solve computes for
+ * mdivide_left_tri (stan/math/prim/mat/fun/mdivide_left_tri.hpp:34-36, 75; rev: stan/math/rev/mat/fun/mdivide_left_tri.hpp
+ * :78, :98-101).  lower: the lower triangle of a is read, else the upper; trans: op(A) = A'. */
+int oracle_tri_solve(int lower, int trans, int64_t n, int64_t m, const double* a, int64_t lda, const double* b, int64_t ldb,
+                     double* x, int64_t ldx) {
+  if (n < 0 || m < 0) return STAN_CUDA_ERR_ARG;
+  const int forward = (lower != 0) != (trans != 0);  /* op(A) is lower triangular */
+  for (int64_t c = 0; c < m; ++c) {
+    for (int64_t i = 0; i < n; ++i) x[c * ldx + i] = b[c * ldb + i];
+    for (int64_t s = 0; s < n; ++s) {
+      const int64_t i = forward ? s : n - 1 - s;
+      double v = x[c * ldx + i];
+      if (forward) {
+        for (int64_t k = 0; k < i; ++k) v -= (trans ? a[i * lda + k] : a[k * lda + i]) * x[c * ldx + k];
+      } else {
+        for (int64_t k = i + 1; k < n; ++k) v -= (trans ? a[i * lda + k] : a[k * lda + i]) * x[c * ldx + k];
+      }
+      x[c * ldx + i] = v / a[i * lda + i];
+    }
+  }
+  return STAN_CUDA_OK;
+}
+
 /* Vectorised elementwise densities with an integer outcome.
  *   bernoulli_logit_lpmf  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
  *   poisson_log_lpmf      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93

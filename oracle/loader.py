@@ -46,6 +46,8 @@ def oracle_lib():
         lib.oracle_cholesky_decompose.argtypes = [i64, vp_, i64, vp_, i64]
         lib.oracle_cholesky_adjoint.restype = C.c_int
         lib.oracle_cholesky_adjoint.argtypes = [i64, vp_, i64, vp_, i64, vp_, i64]
+        lib.oracle_tri_solve.restype = C.c_int
+        lib.oracle_tri_solve.argtypes = [C.c_int, C.c_int, i64, i64, vp_, i64, vp_, i64, vp_, i64]
         lib.oracle_multiply.restype = C.c_int
         lib.oracle_multiply.argtypes = [C.POINTER(_abi.MultiplyArgs)]
         lib.oracle_density_eval.restype = C.c_int
@@ -96,6 +98,11 @@ def ref_lib():
             lib.stanref_cholesky.argtypes = [l, dp, dp, dp, C.c_char_p, i]
             lib.stanref_cholesky_rev.restype = i
             lib.stanref_cholesky_rev.argtypes = [l, dp, dp, dp, dp, dp, C.c_char_p, i]
+        if hasattr(lib, "stanref_mdivide_left_tri"):
+            lib.stanref_mdivide_left_tri.restype = i
+            lib.stanref_mdivide_left_tri.argtypes = [i, l, l, dp, dp, dp, dp, C.c_char_p, i]
+            lib.stanref_mdivide_left_tri_rev.restype = i
+            lib.stanref_mdivide_left_tri_rev.argtypes = [i, i, l, l, dp, dp, dp, dp, dp, dp, dp, C.c_char_p, i]
         lib.stanref_init_threads.restype = i
         lib.stanref_init_threads.argtypes = [i]
         lib.stanref_shards_create.restype = C.c_void_p
@@ -625,3 +632,40 @@ def ref_cholesky_rev(a, w):
     if rc != 0:
         raise RefError(rc, err.value.decode())
     return {"l": l, "a_adj": a_adj, "forward_s": float(secs[0]), "grad_s": float(secs[1])}
+
+
+# ------------------------------------------------------------------------------------------
+# triangular solve (mdivide_left_tri)
+def oracle_tri_solve(a, b, lower=True, trans=False):
+    """op(A)^-1 b by plain-C substitution; b a matrix or a vector."""
+    a, b = _fmat(a), _fmat(b)
+    n, m = a.shape[0], b.shape[1]
+    x = np.zeros((n, m), order="F")
+    rc = oracle_lib().oracle_tri_solve(int(lower), int(trans), n, m, a.ctypes.data, max(n, 1), b.ctypes.data, max(n, 1),
+                                       x.ctypes.data, max(n, 1))
+    assert rc == 0
+    return x
+
+
+def ref_mdivide_left_tri(a, b, lower=True):
+    a, b = _fmat(a), _fmat(b)
+    n, m = a.shape[0], b.shape[1]
+    x, secs = np.zeros((n, m), order="F"), np.zeros(1)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_mdivide_left_tri(int(lower), n, m, a.ctypes.data, b.ctypes.data, x.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return x, float(secs[0])
+
+
+def ref_mdivide_left_tri_rev(a, b, w, lower=True, var_mask=3):
+    a, b, w = _fmat(a), _fmat(b), _fmat(w)
+    n, m = a.shape[0], b.shape[1]
+    x, da, db, secs = np.zeros((n, m), order="F"), np.zeros((n, n), order="F"), np.zeros((n, m), order="F"), np.zeros(2)
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_mdivide_left_tri_rev(int(lower), int(var_mask), n, m, a.ctypes.data, b.ctypes.data, w.ctypes.data,
+                                                x.ctypes.data, da.ctypes.data, db.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    return {"x": x, "da": da if var_mask & 1 else None, "db": db if var_mask & 2 else None,
+            "forward_s": float(secs[0]), "grad_s": float(secs[1])}

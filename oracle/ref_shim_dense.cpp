@@ -150,4 +150,59 @@ int stanref_cholesky_rev(long n, const double* a, const double* w, double* l, do
       err, errlen);
 }
 
+// X = mdivide_left_tri<Lower | Upper>(A, B) for double matrices (prim/mat/fun/mdivide_left_tri.hpp:58-77)
+int stanref_mdivide_left_tri(int lower, long n, long m, const double* a, const double* b, double* x, double* seconds, char* err,
+                             int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d A = Eigen::Map<const matrix_d>(a, n, n), B = Eigen::Map<const matrix_d>(b, n, m);
+        auto t0 = std::chrono::steady_clock::now();
+        matrix_d X = lower ? stan::math::mdivide_left_tri<Eigen::Lower>(A, B) : stan::math::mdivide_left_tri<Eigen::Upper>(A, B);
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+        Eigen::Map<matrix_d>(x, n, m) = X;
+      },
+      err, errlen);
+}
+
+// Reverse mode (rev/mat/fun/mdivide_left_tri.hpp: the vv / dv / vd nodes): X = mdivide_left_tri(A, B) with A and / or B
+// matrices of var (var_mask bit 0: A, bit 1: B), f = sum(W * X): da (the triangle that is an operand, zeros
+// elsewhere) and db.  seconds[0]: forward, seconds[1]: grad().
+int stanref_mdivide_left_tri_rev(int lower, int var_mask, long n, long m, const double* a, const double* b, const double* w,
+                                 double* x, double* da, double* db, double* seconds, char* err, int errlen) {
+  return guarded(
+      [&]() {
+        matrix_d A = Eigen::Map<const matrix_d>(a, n, n), B = Eigen::Map<const matrix_d>(b, n, m);
+        matrix_v Av, Bv, Xv;
+        if (var_mask & 1) Av = to_var(A);
+        if (var_mask & 2) Bv = to_var(B);
+        auto t0 = std::chrono::steady_clock::now();
+#define STANREF_TRI(UPLO)                                                                          \
+  ((var_mask & 3) == 3 ? stan::math::mdivide_left_tri<UPLO>(Av, Bv)                                \
+                       : (var_mask & 1) ? stan::math::mdivide_left_tri<UPLO>(Av, B) : stan::math::mdivide_left_tri<UPLO>(A, Bv))
+        if (!(var_mask & 3)) throw std::invalid_argument("stanref_mdivide_left_tri_rev: no variable operand");
+        if (lower) Xv = STANREF_TRI(Eigen::Lower); else Xv = STANREF_TRI(Eigen::Upper);
+#undef STANREF_TRI
+        auto t1 = std::chrono::steady_clock::now();
+        std::vector<var> ops(Xv.data(), Xv.data() + Xv.size());
+        std::vector<double> grads(w, w + n * m);
+        double val = 0;
+        for (long i = 0; i < n * m; ++i) val += w[i] * Xv(i).val();
+        var f = stan::math::precomputed_gradients(val, ops, grads);
+        auto t2 = std::chrono::steady_clock::now();
+        f.grad();
+        auto t3 = std::chrono::steady_clock::now();
+        if (seconds) {
+          seconds[0] = std::chrono::duration<double>(t1 - t0).count();
+          seconds[1] = std::chrono::duration<double>(t3 - t2).count();
+        }
+        for (long i = 0; i < n * m; ++i) x[i] = Xv(i).val();
+        if ((var_mask & 1) && da)
+          for (long i = 0; i < n * n; ++i) da[i] = Av(i).adj();
+        if ((var_mask & 2) && db)
+          for (long i = 0; i < n * m; ++i) db[i] = Bv(i).adj();
+      },
+      err, errlen);
+}
+
 }  // extern "C"

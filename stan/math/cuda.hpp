@@ -22,6 +22,8 @@
 #include <stan/math/cuda/rev_multiply.hpp>
 #include <stan/math/cuda/cholesky_decompose.hpp>
 #include <stan/math/cuda/rev_cholesky_decompose.hpp>
+#include <stan/math/cuda/mdivide_left_tri.hpp>
+#include <stan/math/cuda/rev_mdivide_left_tri.hpp>
 #include <stan/math/cuda/map_rect_devices.hpp>
 #endif
 #endif

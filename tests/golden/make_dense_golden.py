@@ -78,6 +78,35 @@ t = np.linspace(0, 3, 60)
 add_chol("gp_60", 0.75 ** 2 * np.exp(-0.5 * (t[:, None] - t[None, :]) ** 2 / 0.5 ** 2) + 1e-4 * np.eye(60))
 out["chol_cases"] = np.array(chol_names)
 
+# ---- mdivide_left_tri: solve and reverse sweep (rev/mat/fun/mdivide_left_tri.hpp) for f = sum(W * X)
+tri_names = []
+
+
+def add_tri(name, a, b, lower):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    rng = np.random.default_rng(2000 + len(tri_names))
+    w = rng.uniform(-1, 1, b.shape)
+    p = "tri/%s/" % name
+    x, _ = L.ref_mdivide_left_tri(a, b, lower)
+    r = L.ref_mdivide_left_tri_rev(a, b, w, lower, 3)
+    assert np.array_equal(r["x"], x)
+    for mask in (1, 2):   # the adjoint of an operand does not depend on whether the other one is a variable (the
+        q = L.ref_mdivide_left_tri_rev(a, b, w, lower, mask)   # three nodes of the reference differ in rounding only)
+        got, want = (q["da"], r["da"]) if mask == 1 else (q["db"], r["db"])
+        assert np.max(np.abs(got - want)) <= 1e-13 * np.max(np.abs(want))
+    out[p + "a"], out[p + "b"], out[p + "w"], out[p + "lower"] = a, b, w, np.array(int(lower))
+    out[p + "x"], out[p + "da"], out[p + "db"] = x, r["da"], r["db"]
+    tri_names.append(name)
+
+
+for (n, m) in ((1, 1), (3, 2), (63, 9), (65, 17), (130, 40)):
+    a = rng.uniform(-5, 5, (n, n))   # the reference's fixture (rev/mat/fun/mdivide_left_tri_test.cpp:131-140): diagonal 20
+    a[np.diag_indices(n)] = 20.0
+    b = rng.uniform(-5, 5, (n, m))
+    add_tri("lower_%dx%d" % (n, m), a, b, True)
+    add_tri("upper_%dx%d" % (n, m), a, b, False)
+out["tri_cases"] = np.array(tri_names)
+
 out["cases"] = np.array(names)
 np.savez_compressed(os.path.join(ROOT, "tests", "golden", "dense_golden.npz"), **out)
-print("wrote %d multiply cases, %d cholesky cases" % (len(names), len(chol_names)))
+print("wrote %d multiply, %d cholesky, %d triangular-solve cases" % (len(names), len(chol_names), len(tri_names)))

@@ -27,6 +27,7 @@ int oracle_glm_eval(const stan_cuda_glm_args* a);
 int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a);
 int oracle_student_t_lpdf_eval(const stan_cuda_student_t_args* a);
 int oracle_multiply(const stan_cuda_multiply_args* g);
+int oracle_tri_solve(int lower, int trans, int64_t n, int64_t m, const double* a, int64_t lda, const double* b, int64_t ldb, double* x, int64_t ldx);
 int oracle_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl);
 int oracle_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda);
 int oracle_density_eval(const stan_cuda_density_args* a);
@@ -238,6 +239,14 @@ int stan_cuda_multiply(const stan_cuda_multiply_args* g) {
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
   TIMED(oracle_multiply(g));
   return rc < 0 ? fail(rc, "stan_cuda_multiply: bad argument") : rc;
+}
+
+int stan_cuda_tri_solve(int lower, int trans, int64_t n, int64_t m, const double* a, int64_t lda, const double* b, int64_t ldb,
+                        double* x, int64_t ldx) {
+  if (n < 0 || m < 0 || (n > 0 && !a) || (n > 0 && m > 0 && (!b || !x))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_tri_solve: bad argument");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  if (x == b) { /* the oracle copies b into x first: aliasing is fine */ }
+  return oracle_tri_solve(lower, trans, n, m, a, lda, b, ldb, x, ldx);
 }
 
 int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {

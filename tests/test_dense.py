@@ -105,6 +105,32 @@ def test_oracle_cholesky_rejects_what_the_reference_rejects():
                 L.ref_cholesky(bad)
 
 
+def _tri_case(g, name):
+    p = "tri/%s/" % name
+    c = {k: g[p + k] for k in ("a", "b", "w", "x", "da", "db")}
+    c["lower"] = bool(g[p + "lower"])
+    return c
+
+
+def _check_tri(solve, c, tol, what):
+    """x = A^-1 b, adjB = A^-T w, adjA = -(adjB x') on the operand triangle (rev/mat/fun/mdivide_left_tri.hpp:98-119)"""
+    lower, a = c["lower"], c["a"]
+    x = solve(a, c["b"], lower, False)
+    assert np.max(np.abs(x - c["x"])) <= tol * np.max(np.abs(c["x"])), what
+    adj_b = solve(a, c["w"], lower, True)
+    assert np.max(np.abs(adj_b - c["db"])) <= tol * np.max(np.abs(c["db"])), what
+    bound = np.abs(c["db"]) @ np.abs(c["x"]).T
+    adj_a = -(adj_b @ x.T)
+    adj_a = np.tril(adj_a) if lower else np.triu(adj_a)
+    assert np.max(np.abs(adj_a - c["da"]) / np.where(bound > 0, bound, 1.0)) <= tol, what
+
+
+def test_oracle_tri_solve_matches_golden(golden_mm):
+    assert len(golden_mm["tri_cases"]) >= 10
+    for name in golden_mm["tri_cases"]:
+        _check_tri(lambda a, b, lower, trans: L.oracle_tri_solve(a, b, lower, trans), _tri_case(golden_mm, str(name)), 1e-12, name)
+
+
 # ------------------------------------------------------------------------------------------ GPU
 @pytest.fixture(scope="module")
 def dense():
@@ -128,7 +154,7 @@ def test_device_matches_golden(dense, golden_mm):
 
 SHAPES = [(1, 1, 1), (1, 7, 1), (2, 3, 4), (63, 8, 65), (64, 7, 64), (64, 9, 64), (65, 16, 63), (127, 33, 129), (128, 128, 128),
           (129, 130, 131), (255, 17, 257), (300, 1, 300), (1, 300, 1), (5, 1000, 3), (1000, 5, 3), (3, 5, 1000), (513, 64, 700),
-          (2048, 24, 1500)]
+          (2048, 24, 1500), (64, 5000, 130), (1, 3000, 1), (100, 1024, 100)]   # the last three: split-K
 
 
 @pytest.mark.gpu
@@ -277,3 +303,48 @@ def test_cholesky_full_size_properties(dense):
     # the operands are the lower triangle of A only: a symmetric perturbation moves (i, j) and (j, i) together
     analytic = np.sum(a_adj * np.tril(e))
     assert abs(fd - analytic) <= 1e-6 * max(abs(analytic), 1.0)
+
+
+# ---- mdivide_left_tri --------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_device_tri_solve_matches_golden(dense, golden_mm):
+    for name in golden_mm["tri_cases"]:
+        _check_tri(lambda a, b, lower, trans: dense.tri_solve(a, b, lower, trans), _tri_case(golden_mm, str(name)), 1e-10, name)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,m", [(1, 1), (2, 5), (63, 64), (64, 1), (65, 130), (128, 128), (129, 7), (300, 300), (1000, 33)])
+def test_device_tri_solve_matches_oracle(dense, n, m):
+    rng = np.random.default_rng(n * 1009 + m)
+    a = rng.uniform(-5, 5, (n, n))
+    a[np.diag_indices(n)] = max(20.0, 0.6 * n)
+    b = rng.uniform(-5, 5, (n, m))
+    for lower in (True, False):
+        for trans in (False, True):
+            ref = L.oracle_tri_solve(a, b, lower, trans)
+            got = dense.tri_solve(a, b, lower, trans)
+            assert np.max(np.abs(got - ref)) <= 1e-10 * np.max(np.abs(ref)), (lower, trans)
+    v = b[:, 0].copy()
+    assert np.max(np.abs(dense.tri_solve(a, v) - L.oracle_tri_solve(a, v)[:, 0])) <= 1e-10 * np.max(np.abs(v))
+
+
+@pytest.mark.gpu
+def test_tri_solve_full_size_properties(dense):
+    """n = 4096, 512 right-hand sides: the residual op(A) x - b is at rounding level, the other triangle is never read
+    (poisoned with NaN), and solving against the identity gives the inverse (A A^-1 = I)."""
+    rng = np.random.default_rng(4)
+    n, m = 4096, 512
+    a = rng.uniform(-1, 1, (n, n))
+    a[np.diag_indices(n)] = 0.05 * n
+    b = rng.uniform(-1, 1, (n, m))
+    for lower in (True, False):
+        tri = np.tril(a) if lower else np.triu(a)
+        poisoned = np.where(tri != 0, tri, np.nan)
+        for trans in (False, True):
+            x = dense.tri_solve(poisoned, b, lower, trans)
+            op = tri.T if trans else tri
+            assert np.max(np.abs(op @ x - b)) <= 1e-12 * n ** 0.5 * np.max(np.abs(b)) * 10
+    inv = dense.tri_solve(a, np.eye(n), True, False)
+    assert np.max(np.abs(np.tril(a) @ inv - np.eye(n))) <= 1e-11
+    with pytest.raises(ValueError, match="must match in size"):
+        dense.tri_solve(a, np.zeros((5, 2)))

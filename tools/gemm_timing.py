@@ -19,7 +19,8 @@ shapes = [(1024, 1024, 1024), (2048, 2048, 2048), (4096, 4096, 4096), (8192, 819
 if len(sys.argv) > 1:
     shapes = [tuple(int(v) for v in s.split("x")) for s in sys.argv[1:]]
 for (m, k, n) in shapes:
-    a, b = rng.standard_normal((m, k)), rng.standard_normal((k, n))
+    # column-major like the Eigen matrices of the callers (a C-ordered numpy array would be transposed on every call)
+    a, b = np.asfortranarray(rng.standard_normal((m, k))), np.asfortranarray(rng.standard_normal((k, n)))
     da, db = dense.MatrixCuda(a), dense.MatrixCuda(b)
     for _ in range(2):
         c = da @ db
@@ -38,6 +39,19 @@ for (m, k, n) in shapes:
     c = dat.T @ db
     line["transposed_a_ms"] = 1e3 * (time.perf_counter() - t0)
     del c, dat
+    # the two directions of the host <-> device path on their own: upload of a touched matrix, download into a fresh
+    # (never touched) array and into one that has been written before
+    t0 = time.perf_counter()
+    tmp = dense.MatrixCuda(a)
+    line["upload_a_ms"] = 1e3 * (time.perf_counter() - t0)
+    line["upload_a_gbs"] = a.nbytes / (time.perf_counter() - t0) / 1e9
+    t0 = time.perf_counter()
+    fresh = tmp.to_host()
+    line["download_fresh_ms"] = 1e3 * (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    tmp.to_host(out=fresh)
+    line["download_touched_ms"] = 1e3 * (time.perf_counter() - t0)
+    del tmp, fresh
     ts = []
     for _ in range(3):
         t0 = time.perf_counter()
