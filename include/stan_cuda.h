@@ -338,6 +338,15 @@ STAN_CUDA_API int stan_cuda_multiply(const stan_cuda_multiply_args* a);
  * adjoint: given l and the adjoints l_adj of its lower triangle, writes the adjoints of the lower triangle of a into
  *   a_adj (n x n, zeros above the diagonal: only the lower triangle of a is an operand of the reference's node). */
 STAN_CUDA_API int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl);
+/* Squared-exponential covariance (the gp_exp_quad_cov hooks of
+ * stan/math/prim/mat/fun/gp_exp_quad_cov.hpp:344-655, OpenCL kernels stan/math/opencl/kernels/gp_exp_quad_cov.hpp):
+ *   cov(i, j) = sigma_sq * exp(factor * sum_d (x1[d][i] - x2[d][j])^2),   cov n1 x n2 column-major, host memory.
+ * Points are stored dimension-major: coordinate d of point i at x[d * n + i] (a std::vector<double> of scalars is
+ * dim = 1).  x2 == NULL: the one-sample form, cov is n1 x n1 with sigma_sq exactly on its diagonal (:53, :88).
+ * factor = -0.5 / l^2 for a scalar length scale; -0.5 when the caller has divided the coordinates by a vector of
+ * length scales (divide_columns, :233, :338).  The caller checks the operands (NaN, positivity) as the reference does. */
+STAN_CUDA_API int stan_cuda_gp_exp_quad_cov(int64_t n1, int64_t n2, int64_t dim, const double* x1, const double* x2,
+                                            double sigma_sq, double factor, double* cov, int64_t ldc);
 /* Triangular solve x (n x m) = op(A)^-1 b (the mdivide_left_tri hooks of
  * stan/math/prim/mat/fun/mdivide_left_tri.hpp:58-100 and stan/math/rev/mat/fun/mdivide_left_tri.hpp:69-82, 91-105,
  * 145-159, 170-183, for which the OpenCL backend has tri_inverse + multiply, stan/math/opencl/tri_inverse.hpp).

@@ -175,6 +175,8 @@ PROTOTYPES = {
     "stan_cuda_matrix_multiply": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "stan_cuda_multiply": (C.c_int, [C.POINTER(MultiplyArgs)]),
     "stan_cuda_cholesky_decompose": (C.c_int, [C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
+    "stan_cuda_gp_exp_quad_cov": (C.c_int, [C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
+                                            C.c_void_p, C.c_int64]),
     "stan_cuda_tri_solve": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                       C.c_void_p, C.c_int64]),
     "stan_cuda_cholesky_adjoint": (C.c_int, [C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),

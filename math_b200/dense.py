@@ -135,3 +135,24 @@ def tri_solve(a, b, lower=True, trans=False):
     check(lib().stan_cuda_tri_solve(int(lower), int(trans), n, m, a.ctypes.data, max(n, 1), b.ctypes.data, max(n, 1),
                                     x.ctypes.data, max(n, 1)))
     return x[:, 0] if vec else x
+
+
+def gp_exp_quad_cov(x1, sigma, length_scale, x2=None):
+    """Squared-exponential covariance sigma^2 exp(-|x1_i - x2_j|^2 / (2 l^2)) (stan_cuda_gp_exp_quad_cov).  x: n scalars or
+    an n x dim array of points; length_scale a scalar or one value per dimension (the points are then divided by it
+    first, as the reference's divide_columns does).  x2 = None: the one-sample form (exact sigma^2 on the diagonal)."""
+    def pack(x):
+        x = np.asarray(x, dtype=np.float64)
+        pts = x.reshape(-1, 1) if x.ndim == 1 else x
+        if np.ndim(length_scale) > 0:
+            pts = pts / np.asarray(length_scale, dtype=np.float64)[None, :]
+        return np.ascontiguousarray(pts.T)   # dimension-major: [dim][n]
+    p1 = pack(x1)
+    p2 = None if x2 is None else pack(x2)
+    dim, n1 = p1.shape
+    n2 = n1 if p2 is None else p2.shape[1]
+    factor = -0.5 if np.ndim(length_scale) > 0 else -0.5 / (float(length_scale) * float(length_scale))
+    cov = np.zeros((n1, n2), order="F")
+    check(lib().stan_cuda_gp_exp_quad_cov(n1, n2, dim, p1.ctypes.data, None if p2 is None else p2.ctypes.data,
+                                          float(sigma) * float(sigma), factor, cov.ctypes.data, max(n1, 1)))
+    return cov

@@ -514,6 +514,33 @@ int oracle_tri_solve(int lower, int trans, int64_t n, int64_t m, const double* a
   return STAN_CUDA_OK;
 }
 
+/* Squared-exponential covariance: internal::gp_exp_quad_cov of
+ * stan/math/prim/mat/fun/gp_exp_quad_cov.hpp:40-170 -- cov(i, j) = sigma_sq * exp(squared_distance(x1_i, x2_j) * factor),
+ * the diagonal of the one-sample form (x2 == NULL) set to sigma_sq (:53, :88).  Points dimension-major. */
+int oracle_gp_exp_quad_cov(int64_t n1, int64_t n2, int64_t dim, const double* x1, const double* x2, double sigma_sq, double factor,
+                           double* cov, int64_t ldc) {
+  if (n1 < 0 || n2 < 0 || dim < 1) return STAN_CUDA_ERR_ARG;
+  const int symmetric = x2 == NULL;
+  if (symmetric) {
+    x2 = x1;
+    n2 = n1;
+  }
+  for (int64_t j = 0; j < n2; ++j)
+    for (int64_t i = 0; i < n1; ++i) {
+      if (symmetric && i == j) {
+        cov[j * ldc + i] = sigma_sq;
+        continue;
+      }
+      double d2 = 0.0;
+      for (int64_t d = 0; d < dim; ++d) {
+        const double diff = x1[d * n1 + i] - x2[d * n2 + j];
+        d2 += diff * diff;
+      }
+      cov[j * ldc + i] = sigma_sq * exp(d2 * factor);
+    }
+  return STAN_CUDA_OK;
+}
+
 /* Vectorised elementwise densities with an integer outcome.
  *   bernoulli_logit_lpmf  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
  *   poisson_log_lpmf      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93

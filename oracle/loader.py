@@ -48,6 +48,8 @@ def oracle_lib():
         lib.oracle_cholesky_adjoint.argtypes = [i64, vp_, i64, vp_, i64, vp_, i64]
         lib.oracle_tri_solve.restype = C.c_int
         lib.oracle_tri_solve.argtypes = [C.c_int, C.c_int, i64, i64, vp_, i64, vp_, i64, vp_, i64]
+        lib.oracle_gp_exp_quad_cov.restype = C.c_int
+        lib.oracle_gp_exp_quad_cov.argtypes = [i64, i64, i64, vp_, vp_, C.c_double, C.c_double, vp_, i64]
         lib.oracle_multiply.restype = C.c_int
         lib.oracle_multiply.argtypes = [C.POINTER(_abi.MultiplyArgs)]
         lib.oracle_density_eval.restype = C.c_int
@@ -669,3 +671,25 @@ def ref_mdivide_left_tri_rev(a, b, w, lower=True, var_mask=3):
         raise RefError(rc, err.value.decode())
     return {"x": x, "da": da if var_mask & 1 else None, "db": db if var_mask & 2 else None,
             "forward_s": float(secs[0]), "grad_s": float(secs[1])}
+
+
+# ------------------------------------------------------------------------------------------
+# gp_exp_quad_cov
+def oracle_gp_exp_quad_cov(x1, sigma, length_scale, x2=None):
+    """internal::gp_exp_quad_cov restated (oracle/glm_oracle.c); argument meaning as math_b200.dense.gp_exp_quad_cov"""
+    def pack(x):
+        x = np.asarray(x, dtype=np.float64)
+        pts = x.reshape(-1, 1) if x.ndim == 1 else x
+        if np.ndim(length_scale) > 0:
+            pts = pts / np.asarray(length_scale, dtype=np.float64)[None, :]
+        return np.ascontiguousarray(pts.T)
+    p1 = pack(x1)
+    p2 = None if x2 is None else pack(x2)
+    dim, n1 = p1.shape
+    n2 = n1 if p2 is None else p2.shape[1]
+    factor = -0.5 if np.ndim(length_scale) > 0 else -0.5 / (float(length_scale) * float(length_scale))
+    cov = np.zeros((n1, n2), order="F")
+    rc = oracle_lib().oracle_gp_exp_quad_cov(n1, n2, dim, p1.ctypes.data, None if p2 is None else p2.ctypes.data,
+                                             float(sigma) * float(sigma), factor, cov.ctypes.data, max(n1, 1))
+    assert rc == 0
+    return cov

@@ -24,6 +24,7 @@
 #include <stan/math/cuda/rev_cholesky_decompose.hpp>
 #include <stan/math/cuda/mdivide_left_tri.hpp>
 #include <stan/math/cuda/rev_mdivide_left_tri.hpp>
+#include <stan/math/cuda/gp_exp_quad_cov.hpp>
 #include <stan/math/cuda/map_rect_devices.hpp>
 #endif
 #endif

@@ -123,6 +123,27 @@ INSTANTIATE_TEST_CASE_P(Shapes, CudaTriSolve,
                                           std::make_pair(1, 8), std::make_pair(63, 9), std::make_pair(64, 64), std::make_pair(65, 17),
                                           std::make_pair(130, 300), std::make_pair(513, 40), std::make_pair(700, 8)));
 
+TEST(CudaTriSolveRouting, mdivide_right_tri_matches_reference) {
+  // x = b A^-1 (prim/mat/fun/mdivide_right_tri.hpp:57-80), solved on the device as x' = A^-T b'
+  for (int n : {256, 300, 517}) {
+    MatrixXd A = tri_fixture(n, 40 + n), b = uniform_matrix(33, n, 50 + n);
+    const uint64_t before = device_calls();
+    MatrixXd xl = stan::math::mdivide_right_tri<Eigen::Lower>(b, A), xu = stan::math::mdivide_right_tri<Eigen::Upper>(b, A);
+    EXPECT_GT(device_calls(), before);
+    EXPECT_LE(rel_err(xl, stan::math::mdivide_right_tri_reference_cpu<Eigen::Lower>(b, A)), 1e-10) << n;
+    EXPECT_LE(rel_err(xu, stan::math::mdivide_right_tri_reference_cpu<Eigen::Upper>(b, A)), 1e-10) << n;
+    MatrixXd low = stan::math::mdivide_right_tri_low(b, A);
+    EXPECT_LE(rel_err(low, xl), 1e-14);
+  }
+  MatrixXd A5 = tri_fixture(5, 1), b_bad = uniform_matrix(9, 4, 2);
+  EXPECT_THROW(stan::math::mdivide_right_tri<Eigen::Lower>(b_bad, A5), std::invalid_argument);
+  // var arguments stay on the reference's generic template
+  matrix_v Av = to_v(tri_fixture(6, 3)), bv = to_v(uniform_matrix(2, 6, 4));
+  matrix_v xv = stan::math::mdivide_right_tri<Eigen::Lower>(bv, Av);
+  EXPECT_EQ(2, xv.rows());
+  stan::math::recover_memory();
+}
+
 TEST(CudaTriSolveRouting, inverse_small_systems_and_exceptions) {
   MatrixXd A = tri_fixture(300, 1);
   MatrixXd inv = stan::math::mdivide_left_tri<Eigen::Lower>(A);  // 300 >= 256: device

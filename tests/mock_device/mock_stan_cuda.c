@@ -28,6 +28,7 @@ int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a);
 int oracle_student_t_lpdf_eval(const stan_cuda_student_t_args* a);
 int oracle_multiply(const stan_cuda_multiply_args* g);
 int oracle_tri_solve(int lower, int trans, int64_t n, int64_t m, const double* a, int64_t lda, const double* b, int64_t ldb, double* x, int64_t ldx);
+int oracle_gp_exp_quad_cov(int64_t n1, int64_t n2, int64_t dim, const double* x1, const double* x2, double sigma_sq, double factor, double* cov, int64_t ldc);
 int oracle_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl);
 int oracle_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda);
 int oracle_density_eval(const stan_cuda_density_args* a);
@@ -247,6 +248,13 @@ int stan_cuda_tri_solve(int lower, int trans, int64_t n, int64_t m, const double
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
   if (x == b) { /* the oracle copies b into x first: aliasing is fine */ }
   return oracle_tri_solve(lower, trans, n, m, a, lda, b, ldb, x, ldx);
+}
+
+int stan_cuda_gp_exp_quad_cov(int64_t n1, int64_t n2, int64_t dim, const double* x1, const double* x2, double sigma_sq, double factor,
+                              double* cov, int64_t ldc) {
+  if (n1 < 0 || n2 < 0 || dim < 1 || (n1 > 0 && !x1)) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_gp_exp_quad_cov: bad argument");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  return oracle_gp_exp_quad_cov(n1, n2, dim, x1, x2, sigma_sq, factor, cov, ldc);
 }
 
 int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {

@@ -23,7 +23,8 @@ BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_po
             "cuda_student_t_parity_test", "cuda_student_t_distr_test", "ref_student_t_log_test",
             "cuda_multiply_test", "ref_multiply_test", "ref_mix_multiply_test",
             "cuda_cholesky_test", "ref_cholesky_decompose_test", "ref_mix_cholesky_decompose_test",
-            "cuda_tri_solve_test", "ref_mdivide_left_tri_test", "ref_mix_mdivide_left_tri_test"]
+            "cuda_tri_solve_test", "ref_mdivide_left_tri_test", "ref_mdivide_right_tri_test", "ref_mix_mdivide_left_tri_test",
+            "cuda_gp_exp_quad_cov_test", "ref_gp_exp_quad_cov_test", "ref_rev_gp_exp_quad_cov_test"]
 
 
 @pytest.mark.gpu

@@ -131,6 +131,21 @@ def test_oracle_tri_solve_matches_golden(golden_mm):
         _check_tri(lambda a, b, lower, trans: L.oracle_tri_solve(a, b, lower, trans), _tri_case(golden_mm, str(name)), 1e-12, name)
 
 
+def test_oracle_gp_exp_quad_cov_known_values():
+    """the fixture of the reference's test (test/unit/math/prim/mat/fun/gp_exp_quad_cov_test.cpp: x = (-2, -1, -0.5),
+    sigma = 0.2, l = 5: cov(i, j) = sigma^2 exp(-(x_i - x_j)^2 / (2 l^2))) and the two-sample / per-dimension forms
+    against the closed formula; the C++ binaries pin the same function against the compiled reference"""
+    x = np.array([-2.0, -1.0, -0.5])
+    cov = L.oracle_gp_exp_quad_cov(x, 0.2, 5.0)
+    want = 0.04 * np.exp(-0.5 * (x[:, None] - x[None, :]) ** 2 / 25.0)
+    assert np.max(np.abs(cov - want)) <= 1e-17 and np.all(np.diag(cov) == 0.2 * 0.2)
+    rng = np.random.default_rng(1)
+    p1, p2, ls = rng.standard_normal((7, 3)), rng.standard_normal((5, 3)), np.array([0.7, 1.3, 2.0])
+    cross = L.oracle_gp_exp_quad_cov(p1, 1.5, ls, p2)
+    d2 = (((p1[:, None, :] - p2[None, :, :]) / ls) ** 2).sum(-1)
+    assert np.max(np.abs(cross - 2.25 * np.exp(-0.5 * d2))) <= 1e-15
+
+
 # ------------------------------------------------------------------------------------------ GPU
 @pytest.fixture(scope="module")
 def dense():
@@ -348,3 +363,35 @@ def test_tri_solve_full_size_properties(dense):
     assert np.max(np.abs(np.tril(a) @ inv - np.eye(n))) <= 1e-11
     with pytest.raises(ValueError, match="must match in size"):
         dense.tri_solve(a, np.zeros((5, 2)))
+
+
+# ---- gp_exp_quad_cov ---------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("n1,n2,dim", [(1, 1, 1), (3, 3, 1), (31, 33, 2), (300, 300, 1), (257, 129, 3), (1000, 40, 5)])
+def test_device_gp_exp_quad_cov_matches_oracle(dense, n1, n2, dim):
+    rng = np.random.default_rng(n1 * 31 + n2 * 7 + dim)
+    x1, x2 = rng.uniform(-2, 2, (n1, dim)), rng.uniform(-2, 2, (n2, dim))
+    if dim == 1:
+        x1, x2 = x1[:, 0], x2[:, 0]
+    ls = rng.uniform(0.5, 2.0, dim)
+    for length_scale in (0.8, ls) if dim > 1 else (0.8,):
+        ref = L.oracle_gp_exp_quad_cov(x1, 1.3, length_scale)
+        got = dense.gp_exp_quad_cov(x1, 1.3, length_scale)
+        assert np.max(np.abs(got - ref)) <= 1e-10 * np.max(np.abs(ref))
+        assert np.array_equal(got, got.T) and np.all(np.diag(got) == 1.3 * 1.3)
+        ref = L.oracle_gp_exp_quad_cov(x1, 1.3, length_scale, x2)
+        got = dense.gp_exp_quad_cov(x1, 1.3, length_scale, x2)
+        assert np.max(np.abs(got - ref)) <= 1e-10 * np.max(np.abs(ref))
+
+
+@pytest.mark.gpu
+def test_gp_exp_quad_cov_feeds_cholesky_at_full_size(dense):
+    """n = 4096 points on a line: the covariance is symmetric with sigma^2 on the diagonal, entries decay with distance,
+    and with jitter it is positive definite for the device Cholesky (the GP pipeline the hooks exist for)."""
+    n = 4096
+    x = np.linspace(0.0, 40.0, n)
+    cov = dense.gp_exp_quad_cov(x, 0.75, 0.5)
+    assert np.array_equal(cov, cov.T) and np.all(np.diag(cov) == 0.75 * 0.75)
+    assert abs(cov[0, 1] - 0.5625 * np.exp(-0.5 * (x[1] - x[0]) ** 2 / 0.25)) <= 1e-15
+    l = dense.cholesky_decompose(cov + 1e-6 * np.eye(n))
+    assert np.max(np.abs(dense.multiply_host(l, l, trans_b=True) - cov - 1e-6 * np.eye(n))) <= 1e-12
