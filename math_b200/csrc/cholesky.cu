@@ -34,18 +34,25 @@ constexpr int kThreads = 256;
 __device__ __forceinline__ double& at(double* m, int r, int c) { return m[r * kLD + c]; }
 
 // W = inverse of the lower-triangular jb x jb matrix Lm (both in shared memory, W zero above the diagonal).
-// Thread c solves L x = e_c by forward substitution: at every step all threads read the same L(i, k) row segment.
+// Column c of W solves L x = e_c by forward substitution; four lanes of one warp share a column: they split the dot
+// product of step i, add their parts with two shuffles (fixed order) and lane 0 of the group stores x_i.  (One thread
+// per column was 40 us of dependent FMAs per block -- the longest part of the serial spine of the sweeps.)
 __device__ void tri_inverse_shared(const double* Lm, double* W, int jb, int tid) {
   for (int idx = tid; idx < kNB * kNB; idx += kThreads) at(W, idx / kNB, idx % kNB) = 0.0;
   __syncthreads();
-  if (tid < jb) {
-    const int c = tid;
-    at(W, c, c) = 1.0 / Lm[c * kLD + c];
-    for (int i = c + 1; i < jb; ++i) {
-      double s = 0.0;
-      for (int k = c; k < i; ++k) s = fma(Lm[i * kLD + k], at(W, k, c), s);
-      at(W, i, c) = -s / Lm[i * kLD + i];
+  const int c = tid >> 2, part = tid & 3;  // 64 columns x 4 lanes = 256 threads; a warp holds 8 columns
+  const bool live = c < jb;
+  if (live && part == 0) at(W, c, c) = 1.0 / Lm[c * kLD + c];
+  __syncwarp();
+  for (int i = 1; i < jb; ++i) {  // every column walks the same i: rows i <= c of a column are simply skipped
+    double s = 0.0;
+    if (live && i > c) {
+      for (int k = c + part; k < i; k += 4) s = fma(Lm[i * kLD + k], at(W, k, c), s);
     }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    if (live && i > c && part == 0) at(W, i, c) = -s / Lm[i * kLD + i];
+    __syncwarp();
   }
   __syncthreads();
 }
@@ -84,10 +91,11 @@ __global__ void __launch_bounds__(kThreads) potrf_inv_kernel(const double* __res
     __syncthreads();  // everyone has the pivot before it is overwritten
     for (int i = j + tid; i < jb; i += kThreads) at(D, i, j) = (i == j) ? ljj : at(D, i, j) / ljj;
     __syncthreads();
-    const int nt = jb - j - 1;
-    for (int idx = tid; idx < nt * nt; idx += kThreads) {
-      const int r = j + 1 + idx % nt, c = j + 1 + idx / nt;
-      if (r >= c) at(D, r, c) = fma(-at(D, r, j), at(D, c, j), at(D, r, c));
+    // trailing update of the lower triangle: a 16 x 16 grid of threads strides over (r, c) -- no index divisions
+    for (int c = j + 1 + (tid >> 4); c < jb; c += 16) {
+      const double lcj = at(D, c, j);
+      for (int r = j + 1 + (tid & 15); r < jb; r += 16)
+        if (r >= c) at(D, r, c) = fma(-at(D, r, j), lcj, at(D, r, c));
     }
   }
   __syncthreads();
