@@ -395,3 +395,33 @@ def test_gp_exp_quad_cov_feeds_cholesky_at_full_size(dense):
     assert abs(cov[0, 1] - 0.5625 * np.exp(-0.5 * (x[1] - x[0]) ** 2 / 0.25)) <= 1e-15
     l = dense.cholesky_decompose(cov + 1e-6 * np.eye(n))
     assert np.max(np.abs(dense.multiply_host(l, l, trans_b=True) - cov - 1e-6 * np.eye(n))) <= 1e-12
+
+
+@pytest.mark.gpu
+def test_concurrent_host_threads(dense):
+    """four host threads call the dense entry points at once (per-thread streams and staging buffers, one shared pool
+    of copy helpers): every result equals the single-threaded one bit for bit"""
+    import threading
+    rng = np.random.default_rng(11)
+    a = np.asfortranarray(rng.standard_normal((1500, 1100)))
+    b = np.asfortranarray(rng.standard_normal((1100, 1300)))
+    spd = _spd(900, 12)
+    want_c, want_l = dense.multiply_host(a, b), dense.cholesky_decompose(spd)
+    errors = []
+
+    def work(k):
+        try:
+            for _ in range(3):
+                if k % 2 == 0:
+                    assert np.array_equal(dense.multiply_host(a, b), want_c)
+                else:
+                    assert np.array_equal(dense.cholesky_decompose(spd), want_l)
+        except Exception as e:   # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
