@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|s1|m1|m2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -416,6 +416,40 @@ double multiply_rev_once(const MatrixXd& A, const MatrixXd& B, Result* out) {
   return t1 - t0;
 }
 
+// cholesky_decompose.  prim: L = cholesky_decompose(A) for a double matrix; rev: A a matrix of var,
+// f = sum(L), grad() and the adjoints of the lower triangle of A read back (the factorisation + the reverse sweep).
+template <bool GPU>
+double cholesky_prim_once(const MatrixXd& A, Result* out) {
+  const double t0 = now();
+  MatrixXd L = GPU ? stan::math::cholesky_decompose(A) : stan::math::cholesky_decompose_reference_cpu(A);
+  const double t1 = now();
+  out->lp = L.sum();
+  out->grad = Eigen::Map<VectorXd>(L.data(), std::min<int64_t>(L.size(), 4096));
+  return t1 - t0;
+}
+
+template <bool GPU>
+double cholesky_rev_once(const MatrixXd& A, Result* out) {
+  using namespace stan::math;  // NOLINT
+  typedef Eigen::Matrix<var, Eigen::Dynamic, Eigen::Dynamic> matrix_v;
+  start_nested();
+  matrix_v Av(A.rows(), A.cols());
+  for (int64_t i = 0; i < A.size(); ++i) Av(i) = A(i);
+  const double t0 = now();
+  matrix_v L = GPU ? cholesky_decompose(Av) : cholesky_decompose_reference_cpu(Av);
+  var f = sum(L);
+  grad(f.vi_);
+  out->lp = f.val();
+  const int64_t n = A.rows();
+  out->grad.resize(n * (n + 1) / 2);
+  int64_t pos = 0;
+  for (int64_t j = 0; j < n; ++j)
+    for (int64_t i = j; i < n; ++i) out->grad[pos++] = Av(i, j).adj();
+  const double t1 = now();
+  recover_memory_nested();
+  return t1 - t0;
+}
+
 // vectorised lpmf with an integer outcome and a var vector operand (DENSITY 1: bernoulli_logit_lpmf,
 // 2: poisson_log_lpmf); one evaluation = forward + grad() + reading the N adjoints
 template <bool GPU, int DENSITY>
@@ -555,6 +589,32 @@ int run(int argc, char** argv) {
       std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
     }
     std::printf(", \"flops\": %.6g}\n", (rev ? 6.0 : 2.0) * double(n) * double(n) * double(n));
+    return 0;
+  }
+
+  if (config == "k1" || config == "k2") {
+    const bool rev = config == "k2";
+    const int64_t n = n_override ? n_override : 2048;
+    MatrixXd X(n, n);
+    Rng r(1041);
+    for (int64_t i = 0; i < n * n; ++i) X(i) = r.normal();
+    MatrixXd A = X * X.transpose() / double(n) + MatrixXd::Identity(n, n);
+    A = (0.5 * (A + A.transpose())).eval();
+    Result g, c;
+    auto gpu = [&] { return rev ? cholesky_rev_once<true>(A, &g) : cholesky_prim_once<true>(A, &g); };
+    auto cpu = [&] { return rev ? cholesky_rev_once<false>(A, &c) : cholesky_prim_once<false>(A, &c); };
+    gpu();
+    Timing tg = time_reps(2, reps, 30, gpu);
+    std::printf("\"what\": \"cholesky_decompose n = %lld, %s\", ", (long long)n,
+                rev ? "matrix of var: factorisation + grad() + reading the adjoints" : "matrix of double");
+    print_timing("gpu", tg);
+    if (!no_cpu) {
+      Timing tc = time_reps(0, std::max(std::min(cpu_reps, 3), 2), 60, cpu);
+      std::printf(", ");
+      print_timing("cpu_reference_1_thread", tc);
+      std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
+    }
+    std::printf("}\n");
     return 0;
   }
 

@@ -6,7 +6,7 @@ that identical argument blocks can be handed to the CUDA library and to the CPU 
 """
 import ctypes as C
 
-OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND, LOG_ZERO, NOT_POS_DEF = 0, 1, 2, 3, 4, 5
+OK, NONFINITE, BAD_OUTCOME, BAD_OPERAND, LOG_ZERO, NOT_POS_DEF, NOT_SYMMETRIC = 0, 1, 2, 3, 4, 5, 6
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE = -1, -2, -3, -4
 
 BERNOULLI_LOGIT, POISSON_LOG, NORMAL_ID, NEG_BINOMIAL_2_LOG, ORDERED_LOGISTIC = 0, 1, 2, 3, 4
@@ -174,7 +174,7 @@ PROTOTYPES = {
     "stan_cuda_matrix_download": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "stan_cuda_matrix_multiply": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "stan_cuda_multiply": (C.c_int, [C.POINTER(MultiplyArgs)]),
-    "stan_cuda_cholesky_decompose": (C.c_int, [C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
+    "stan_cuda_cholesky_decompose": (C.c_int, [C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_double]),
     "stan_cuda_gp_exp_quad_cov": (C.c_int, [C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                             C.c_void_p, C.c_int64]),
     "stan_cuda_tri_solve": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,

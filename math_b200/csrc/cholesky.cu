@@ -232,6 +232,28 @@ __global__ void zero_strict_upper_kernel(double* __restrict__ L, int64_t ld, int
     if (r < cc) L[cc * ld + r] = 0.0;
 }
 
+// check_symmetric of the reference (stan/math/prim/mat/err/check_symmetric.hpp:39-46) on the uploaded matrix:
+// flag[1] = 1 when some pair fails  |A(m, n) - A(n, m)| <= tol  (NaN fails, as there).  32 x 32 tiles, the mirrored
+// tile read through shared memory so that both reads are coalesced; only tiles on or below the diagonal work.
+__global__ void __launch_bounds__(256) symmetry_kernel(const double* __restrict__ A, int64_t ld, int64_t n, double tol,
+                                                       int* __restrict__ flag) {
+  if (blockIdx.y > blockIdx.x) return;
+  __shared__ double mirror[32][33];
+  const int64_t r0 = int64_t(blockIdx.x) * 32, c0 = int64_t(blockIdx.y) * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8) {  // mirror[j][tx] = A(c0 + tx, r0 + j): the tile across the diagonal
+    const int64_t r = c0 + tx, c = r0 + j;
+    mirror[j][tx] = (r < n && c < n) ? A[c * ld + r] : 0.0;
+  }
+  __syncthreads();
+  bool bad = false;
+  for (int j = ty; j < 32; j += 8) {  // A(r0 + tx, c0 + j) against A(c0 + j, r0 + tx) = mirror[tx][j]
+    const int64_t r = r0 + tx, c = c0 + j;
+    if (r < n && c < n && r > c) bad = bad || !(fabs(A[c * ld + r] - mirror[tx][j]) <= tol);
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag + 1, 1);
+}
+
 struct DeviceBuf {
   double* p = nullptr;
   cudaStream_t stream = nullptr;
@@ -281,7 +303,7 @@ int cholesky_device(int dev, double* A, double* L, int64_t ld, int64_t n, int* i
   return STAN_CUDA_OK;
 }
 
-int cholesky_host(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {
+int cholesky_host(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl, double symmetry_tolerance) {
   NvtxRange range("stan_cuda_cholesky_decompose");
   if (n < 0 || (n > 0 && (!a || !l || lda < n || ldl < n))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_cholesky_decompose: bad argument");
   if (n == 0) return STAN_CUDA_OK;
@@ -300,13 +322,20 @@ int cholesky_host(int64_t n, const double* a, int64_t lda, double* l, int64_t ld
   SC_CUDA(cudaMemsetAsync(info.p, 0, 2 * sizeof(double), td->stream));
   SC_TRY(dense_copy_to_device(A.p, ld, a, lda, n, n, td->stream));
   counters().bytes_uploaded.fetch_add(uint64_t(n) * uint64_t(n) * sizeof(double));
+  if (symmetry_tolerance >= 0.0 && n > 1) {
+    const unsigned tiles = unsigned((n + 31) / 32);
+    symmetry_kernel<<<dim3(tiles, tiles), 256, 0, td->stream>>>(A.p, ld, n, symmetry_tolerance, reinterpret_cast<int*>(info.p));
+    SC_CUDA(cudaGetLastError());
+    counters().launches.fetch_add(1, std::memory_order_relaxed);
+  }
   SC_TRY(cholesky_device(dev, A.p, L.p, ld, n, reinterpret_cast<int*>(info.p), W.p, td->stream));
   SC_TRY(td->reserve_host(8));
   SC_CUDA(cudaMemcpyAsync(td->h_pinned, info.p, sizeof(double), cudaMemcpyDeviceToHost, td->stream));
   SC_TRY(dense_copy_to_host(l, ldl, L.p, ld, n, n, td->stream));  // synchronises
   counters().evals.fetch_add(1, std::memory_order_relaxed);
-  const int info_host = *reinterpret_cast<const int*>(td->h_pinned);
-  return info_host != 0 ? STAN_CUDA_NOT_POS_DEF : STAN_CUDA_OK;
+  const int* info_host = reinterpret_cast<const int*>(td->h_pinned);  // [0]: pivot, [1]: symmetry
+  if (info_host[1] != 0) return STAN_CUDA_NOT_SYMMETRIC;  // the reference checks symmetry first (:60-63)
+  return info_host[0] != 0 ? STAN_CUDA_NOT_POS_DEF : STAN_CUDA_OK;
 }
 
 // a_adj (lower triangle, n x n) = adjoint of A given L and the adjoint of L (lower triangles are read)
@@ -425,8 +454,8 @@ int tri_solve_host(int lower, int trans, int64_t n, int64_t m, const double* a, 
 }  // namespace stancuda
 
 extern "C" {
-int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {
-  return stancuda::cholesky_host(n, a, lda, l, ldl);
+int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl, double symmetry_tolerance) {
+  return stancuda::cholesky_host(n, a, lda, l, ldl, symmetry_tolerance);
 }
 int stan_cuda_cholesky_adjoint(int64_t n, const double* l, int64_t ldl, const double* l_adj, int64_t ldadj, double* a_adj, int64_t lda) {
   return stancuda::cholesky_adjoint_host(n, l, ldl, l_adj, ldadj, a_adj, lda);

@@ -97,14 +97,22 @@ class NotPositiveDefinite(ValueError):
     """cholesky_decompose: the reference throws std::domain_error ("Matrix m is not positive definite")."""
 
 
-def cholesky_decompose(a):
-    """Lower Cholesky factor of a symmetric positive-definite matrix (stan_cuda_cholesky_decompose)."""
+class NotSymmetric(ValueError):
+    """cholesky_decompose: the reference throws std::domain_error ("m is not symmetric")."""
+
+
+def cholesky_decompose(a, symmetry_tolerance=1e-8):
+    """Lower Cholesky factor of a symmetric positive-definite matrix (stan_cuda_cholesky_decompose); the symmetry check
+    of the reference (CONSTRAINT_TOLERANCE = 1e-8) runs on the device; None skips it."""
     a = _fmat(a)
     if a.shape[0] != a.shape[1]:
         raise ValueError("cholesky_decompose: Expecting a square matrix; rows of A (%d) and columns of A (%d) must match in size" % a.shape)
     n = a.shape[0]
     l = np.zeros((n, n), order="F")
-    rc = check(lib().stan_cuda_cholesky_decompose(n, a.ctypes.data, max(n, 1), l.ctypes.data, max(n, 1)))
+    rc = check(lib().stan_cuda_cholesky_decompose(n, a.ctypes.data, max(n, 1), l.ctypes.data, max(n, 1),
+                                                  -1.0 if symmetry_tolerance is None else float(symmetry_tolerance)))
+    if rc == _abi.NOT_SYMMETRIC:
+        raise NotSymmetric("cholesky_decompose: m is not symmetric")
     if rc == _abi.NOT_POS_DEF:
         raise NotPositiveDefinite("cholesky_decompose: Matrix m is not positive definite")
     return l

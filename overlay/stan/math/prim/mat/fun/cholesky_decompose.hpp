@@ -30,12 +30,11 @@ template <>
 inline Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic> cholesky_decompose(
     const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>& m) {
   if (m.rows() >= cuda::cholesky_size_worth_transfer() && m.rows() == m.cols()) {
-    check_symmetric("cholesky_decompose", "m", m);  // :60
     Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic> L;
-    if (cuda::cholesky_on_device(m, L)) {
+    if (cuda::cholesky_on_device(m, L) == STAN_CUDA_OK) {  // symmetric (:60, checked on the device) and positive definite
       return L;
     }
-    // not positive definite: the reference's LLT + check_pos_definite throw its exception
+    // not symmetric or not positive definite: the reference's own checks, in its order, throw its exception
   }
   return cholesky_decompose_reference_cpu(m);
 }

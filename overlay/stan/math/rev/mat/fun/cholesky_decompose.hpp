@@ -35,16 +35,15 @@ namespace math {
 inline Eigen::Matrix<var, -1, -1> cholesky_decompose(const Eigen::Matrix<var, -1, -1>& A) {
 #ifdef STAN_CUDA
   if (A.rows() >= cuda::cholesky_size_worth_transfer() && A.rows() == A.cols()) {
-    check_symmetric("cholesky_decompose", "A", A);  // :404
     Eigen::Matrix<double, -1, -1> A_val(value_of_rec(A));
     Eigen::Matrix<double, -1, -1> L_A;
-    if (cuda::cholesky_on_device(A_val, L_A)) {
+    if (cuda::cholesky_on_device(A_val, L_A) == STAN_CUDA_OK) {  // check_symmetric (:404) runs on the device copy
       cuda::cholesky_cuda* baseVari = new cuda::cholesky_cuda(A, L_A);
       Eigen::Matrix<var, -1, -1> L(A.rows(), A.cols());
       internal::set_lower_tri_coeff_ref(L, baseVari->vari_ref_L_);  // :428-429
       return L;
     }
-    // not positive definite: the reference's LLT + check_pos_definite throw its exception
+    // not symmetric or not positive definite: the reference's own checks, in its order, throw its exception
   }
 #endif
   return cholesky_decompose_reference_cpu(A);

@@ -6,6 +6,7 @@
 #include <stan/math/cuda/err.hpp>
 #include <stan/math/cuda/multiply.hpp>
 #include <stan/math/prim/mat/fun/Eigen.hpp>
+#include <stan/math/prim/mat/err/constraint_tolerance.hpp>
 #include <cstdint>
 
 namespace stan {
@@ -23,15 +24,17 @@ inline int64_t& cholesky_size_worth_transfer() {
 }
 
 /**
- * L = chol(m) on the device (lower, zeros above the diagonal).  Returns false when a pivot is not positive: the
- * caller then runs the reference's LLT + check_pos_definite on the host, which throws the reference's exception.
+ * L = chol(m) on the device (lower, zeros above the diagonal), with the reference's check_symmetric
+ * (prim/mat/err/check_symmetric.hpp, CONSTRAINT_TOLERANCE) evaluated there as well.  Returns the code of the C ABI:
+ * STAN_CUDA_OK, STAN_CUDA_NOT_SYMMETRIC (the caller runs the reference's check_symmetric on the host: it throws the
+ * reference's exception) or STAN_CUDA_NOT_POS_DEF (the caller runs the reference's LLT + check_pos_definite).
  */
-inline bool cholesky_on_device(const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>& m,
-                               Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>& L) {
+inline int cholesky_on_device(const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>& m,
+                              Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>& L) {
   L.resize(m.rows(), m.cols());
-  const int rc = stan_cuda_cholesky_decompose(m.rows(), m.data(), m.rows(), L.data(), L.rows());
+  const int rc = stan_cuda_cholesky_decompose(m.rows(), m.data(), m.rows(), L.data(), L.rows(), CONSTRAINT_TOLERANCE);
   check_cuda_rc("cholesky_decompose", rc);
-  return rc == STAN_CUDA_OK;
+  return rc;
 }
 
 }  // namespace cuda

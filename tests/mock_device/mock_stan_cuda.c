@@ -257,9 +257,13 @@ int stan_cuda_gp_exp_quad_cov(int64_t n1, int64_t n2, int64_t dim, const double*
   return oracle_gp_exp_quad_cov(n1, n2, dim, x1, x2, sigma_sq, factor, cov, ldc);
 }
 
-int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl) {
+int stan_cuda_cholesky_decompose(int64_t n, const double* a, int64_t lda, double* l, int64_t ldl, double symmetry_tolerance) {
   if (n < 0 || (n > 0 && (!a || !l || lda < n || ldl < n))) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_cholesky_decompose: bad argument");
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  if (symmetry_tolerance >= 0.0) /* check_symmetric.hpp:39-46 */
+    for (int64_t m = 0; m < n; ++m)
+      for (int64_t k = m + 1; k < n; ++k)
+        if (!(fabs(a[k * lda + m] - a[m * lda + k]) <= symmetry_tolerance)) return STAN_CUDA_NOT_SYMMETRIC;
   return oracle_cholesky_decompose(n, a, lda, l, ldl);
 }
 

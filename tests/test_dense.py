@@ -284,13 +284,24 @@ def test_device_cholesky_matches_oracle(dense, n):
 
 @pytest.mark.gpu
 def test_device_cholesky_rejects_what_the_reference_rejects(dense):
-    for bad in (-np.eye(3), np.array([[1.0, 2.0], [2.0, 1.0]]), np.array([[1.0, np.nan], [np.nan, 1.0]]), np.zeros((2, 2))):
+    for bad in (-np.eye(3), np.array([[1.0, 2.0], [2.0, 1.0]]), np.array([[np.nan, 0.5], [0.5, 1.0]]), np.zeros((2, 2))):
         with pytest.raises(dense.NotPositiveDefinite):
             dense.cholesky_decompose(bad)
     big = _spd(300, 7)
     big[250, 250] = -1.0    # fails in the fourth block: the flag survives the remaining steps
     with pytest.raises(dense.NotPositiveDefinite):
         dense.cholesky_decompose(big)
+    asym = _spd(200, 8)
+    asym[150, 3] += 1e-6      # beyond CONSTRAINT_TOLERANCE = 1e-8: the device check reports it before any pivot
+    with pytest.raises(dense.NotSymmetric):
+        dense.cholesky_decompose(asym)
+    asym[150, 3] = asym[3, 150] + 1e-10   # inside the tolerance: accepted, the lower triangle is what is factorised
+    assert lower_rel_err(dense.cholesky_decompose(asym), L.oracle_cholesky(asym)[1]) <= 1e-10
+    nan_off = _spd(100, 9)
+    nan_off[40, 7] = np.nan   # NaN fails the symmetry test as in the reference (check_symmetric.hpp:43-44)
+    with pytest.raises(dense.NotSymmetric):
+        dense.cholesky_decompose(nan_off)
+    assert np.array_equal(dense.cholesky_decompose(asym, symmetry_tolerance=None), dense.cholesky_decompose(asym))
     with pytest.raises(ValueError, match="square"):
         dense.cholesky_decompose(np.zeros((2, 3)))
     assert dense.cholesky_decompose(np.zeros((0, 0))).shape == (0, 0)
