@@ -5,6 +5,7 @@
 #include <stan/math/cuda/cholesky_decompose.hpp>
 #include <stan/math/rev/core.hpp>
 #include <stan/math/prim/mat/fun/Eigen.hpp>
+#include <vector>
 
 namespace stan {
 namespace math {
@@ -40,20 +41,29 @@ class cholesky_cuda : public vari {
   }
 
   virtual void chain() {
-    Eigen::MatrixXd L = Eigen::MatrixXd::Zero(M_, M_), L_adj = Eigen::MatrixXd::Zero(M_, M_), A_adj(M_, M_);
+    // three n x n work matrices, kept per thread across evaluations: a fresh Eigen matrix of this size is 32 MB of
+    // page faults at n = 2048, every evaluation, and only the lower triangles are read or written on either side
+    const size_t nn = static_cast<size_t>(M_) * M_;
+    static thread_local std::vector<double> work;
+    if (work.size() < 3 * nn) {
+      work.assign(3 * nn, 0.0);
+    }
+    double* L = work.data();
+    double* L_adj = L + nn;
+    double* A_adj = L_adj + nn;
     size_t pos = 0;
     for (Eigen::Index j = 0; j < M_; ++j) {
       for (Eigen::Index i = j; i < M_; ++i) {
-        L_adj.coeffRef(i, j) = vari_ref_L_[pos]->adj_;
-        L.coeffRef(i, j) = vari_ref_L_[pos]->val_;
+        L_adj[j * M_ + i] = vari_ref_L_[pos]->adj_;
+        L[j * M_ + i] = vari_ref_L_[pos]->val_;
         ++pos;
       }
     }
-    check_cuda_rc("cholesky_decompose", stan_cuda_cholesky_adjoint(M_, L.data(), M_, L_adj.data(), M_, A_adj.data(), M_));
+    check_cuda_rc("cholesky_decompose", stan_cuda_cholesky_adjoint(M_, L, M_, L_adj, M_, A_adj, M_));
     pos = 0;
     for (Eigen::Index j = 0; j < M_; ++j) {
       for (Eigen::Index i = j; i < M_; ++i) {
-        vari_ref_A_[pos++]->adj_ += A_adj.coeffRef(i, j);
+        vari_ref_A_[pos++]->adj_ += A_adj[j * M_ + i];
       }
     }
   }
