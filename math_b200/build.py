@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "math_b200", "csrc")
 LIB_DIR = os.path.join(ROOT, "math_b200", "lib")
 LIB = os.path.join(LIB_DIR, "libstanmath_cuda.so")
-SOURCES = ["glm_fused.cu", "glm_warp.cu", "glm_categorical.cu", "glm_categorical_mma.cu", "glm_categorical_wide.cu", "normal_lpdf.cu", "student_t.cu", "density.cu", "gemm.cu", "cholesky.cu", "gp.cu", "data.cu", "context.cu", "comm.cu", "api.cu"]
+SOURCES = ["glm_fused.cu", "glm_warp.cu", "glm_categorical.cu", "glm_categorical_mma.cu", "glm_categorical_wide.cu", "glm_ordered_wide.cu", "normal_lpdf.cu", "student_t.cu", "density.cu", "gemm.cu", "cholesky.cu", "gp.cu", "data.cu", "context.cu", "comm.cu", "api.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-diag-suppress", "177"]
 

@@ -325,8 +325,6 @@ static int check_glm_args(const stan_cuda_glm_args* a) {
       return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: categorical_logit needs n_classes >= 1 and alpha_len == n_classes");
   } else if (a->family == STAN_CUDA_ORDERED_LOGISTIC) {
     if (a->cuts_len < 0 || (a->cuts_len > 0 && !a->cuts)) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: null cuts");
-    if (a->cuts_len > kMaxCuts)
-      return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: ordered_logistic supports at most 1024 cut-points on the device");
   } else if (!a->alpha || (a->alpha_len != 1 && a->alpha_len != a->n)) {
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_glm_eval: alpha_len must be 1 or n");
   }

@@ -142,6 +142,9 @@ struct LaunchIO {
   // var x: d/dx = d * beta^T streamed out tile by tile (device matrix, column-major rows x k, leading dimension ld_dx)
   double* d_dx = nullptr;
   int64_t ld_dx = 0;
+  // run the block as this family instead of its own (the many-cut-points path of ordered_logistic drives every block of
+  // the matrix as a kFamilyLinearBlock: glm_ordered_wide.cu)
+  int family_override = -1;
 };
 // Internal pseudo-family of the column-block path (k > 512, glm_warp.cu launch_glm_colblocks): a block of columns
 // contributes eta_b = X_b beta_b to a per-row carry vector, or dbeta_b = X_b^T d from a per-row d vector.  Never
@@ -150,7 +153,8 @@ constexpr int kFamilyLinearBlock = 6;
 constexpr int kColBlock = 512;               // columns per block: the widest tile of the warp kernel (C = 32, kc = 16)
 constexpr int kMaxClasses = 16;              // categorical_logit: classes on the device path
 constexpr int kMaxClassWeights = 4096;       // categorical_logit: classes * k_pad (weights live in shared memory)
-constexpr int kMaxCuts = 1024;               // ordered_logistic: per-warp bins and the class table live in shared memory
+constexpr int kMaxCuts = 1024;               // ordered_logistic: up to here the per-warp bins and the class table live in shared
+                                             // memory of the fused kernel; beyond: glm_ordered_wide.cu
 constexpr int kOrdPrivateDoubles = 2048;     // ordered_logistic: ncuts * R up to this -> one private bin row per row slot
 constexpr int kInlineParams = 264;           // covers kpad <= 256 (+ alpha, sigma)
 
@@ -160,6 +164,8 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
 // var x: dx[j * rows + i] = d[i] * params[j]  (d/dx = d * beta^T; data.cu)
 int launch_dx_outer(const double* d_row, const double* d_params, int64_t rows, int64_t k, double* dx, cudaStream_t stream);
 int launch_glm_colblocks(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
+// ordered_logistic with more than kMaxCuts cut-points (glm_ordered_wide.cu)
+int launch_glm_ordered_wide(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical_mma(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);
 int launch_glm_categorical_wide(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream);

@@ -363,18 +363,19 @@ __device__ __forceinline__ void ordered_class_table(const GlmKernelParams& p, do
     tab[4 * ncls + c - 1] = inner ? log1m_exp_dev(cy2 - cy1) : 0.0;
   }
 }
-// one row of class c: t0 = log-density of the row, d = d1 - d2 (location derivative), t2 = d1, t3 = d2
-// (the row's contributions to d/dcuts[c-2] and d/dcuts[c-1], :192-200)
-__device__ __forceinline__ RowTerms ordered_row_epilogue(double loc, int c, int ncls, const double* tab) {
+// one row of a class with cut-points cy1 above and cy2 below it (and ecd, r = 1 / (1 - ecd), l1m = log1m_exp(cy2 - cy1) of
+// the class): t0 = log-density of the row, d = d1 - d2 (location derivative), t2 = d1, t3 = d2 (the row's contributions
+// to d/dcuts[c-2] and d/dcuts[c-1], :192-200)
+__device__ __forceinline__ RowTerms ordered_row_terms(double loc, bool first, bool last, double cy1, double cy2, double ecd,
+                                                      double r, double l1m) {
   RowTerms o;
-  const double cut1 = loc - tab[0 * ncls + c - 1], cut2 = loc - tab[1 * ncls + c - 1];  // :124-125
+  const double cut1 = loc - cy1, cut2 = loc - cy2;  // :124-125
   // exp(-|cut|) serves both the log-density (:128-131) and the derivative: for cut > 0 the reference
   // uses exp(-cut) / (1 + exp(-cut)), else 1 / (1 + exp(cut)) (:165-171) -- the same exponential
   const double e1 = exp_nonpos(-fabs(cut1)), e2 = exp_nonpos(-fabs(cut2));
   const double m1 = (cut1 > 0.0 ? -cut1 : 0.0) - log1p_unit(e1);                     // :128-129
   const double m2 = (cut2 <= 0.0 ? cut2 : 0.0) - log1p_unit(e2);                     // :130-131
-  o.t0 = c == 1 ? m1 : (c == ncls ? m2 : m2 + tab[4 * ncls + c - 1] + m1);            // :137-144
-  const double ecd = tab[2 * ncls + c - 1], r = tab[3 * ncls + c - 1];
+  o.t0 = first ? m1 : (last ? m2 : m2 + l1m + m1);                                    // :137-144
   const double s2 = (cut2 > 0 ? e2 : 1.0) / (1 + e2);                                 // :165-167
   const double s1 = (cut1 > 0 ? e1 : 1.0) / (1 + e1);                                 // :168-171
   const double d1 = s2 + ecd * r;  // s2 - ecd / (ecd - 1)
@@ -383,6 +384,31 @@ __device__ __forceinline__ RowTerms ordered_row_epilogue(double loc, int c, int 
   o.t2 = d1;
   o.t3 = d2;
   return o;
+}
+// the same from the per-CTA class table
+__device__ __forceinline__ RowTerms ordered_row_epilogue(double loc, int c, int ncls, const double* tab) {
+  return ordered_row_terms(loc, c == 1, c == ncls, tab[0 * ncls + c - 1], tab[1 * ncls + c - 1], tab[2 * ncls + c - 1],
+                           tab[3 * ncls + c - 1], tab[4 * ncls + c - 1]);
+}
+
+// d/dcuts bins owned by ONE warp: the active lanes add `val` into bins[key].  Lanes of the warp that hit the same bin are
+// found with match.any; every member adds the group's values in lane order (so the sum does not depend on timing) and
+// the lowest lane of the group makes the one update of that bin -- no floating-point atomics.  All 32 lanes must call.
+__device__ __forceinline__ void warp_bin_add(double* bins, int lane, bool active, int key, double val) {
+  const int mykey = active ? key : -1 - lane;  // inactive lanes form groups of their own
+  const unsigned grp = __match_any_sync(0xffffffffu, mykey);
+  unsigned rem = grp;
+  double acc = 0.0;
+  while (__any_sync(0xffffffffu, rem != 0u)) {
+    const int src = rem ? __ffs(rem) - 1 : lane;
+    const double v = __shfl_sync(0xffffffffu, val, src);
+    if (rem) {
+      acc += v;
+      rem &= rem - 1;
+    }
+  }
+  if (active && lane == __ffs(grp) - 1) bins[key] += acc;
+  __syncwarp();
 }
 
 template <int FAMILY>

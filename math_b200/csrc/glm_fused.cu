@@ -382,7 +382,8 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->blocked = 0;
   p->nb_sums = nullptr;
   p->nb_rowfun = 1;
-  p->ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
+  const int family = io.family_override >= 0 ? io.family_override : d->family;
+  p->ncuts = family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
   p->ord_private = 0;
   p->pair = 0;
   p->pdl = 0;
@@ -412,7 +413,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
   p->host_flag = io.host_flag;
   p->host_seq = io.host_seq;
   const int np = t.kpad + 2 + p->ncuts;
-  if (io.h_params_inline && np <= kInlineParams && d->family != STAN_CUDA_CATEGORICAL_LOGIT) {
+  if (io.h_params_inline && np <= kInlineParams && family != STAN_CUDA_CATEGORICAL_LOGIT) {
     p->inline_n = np;
     for (int i = 0; i < np; ++i) p->inline_params[i] = io.h_params_inline[i];
   } else if (!io.d_params) {
@@ -437,6 +438,7 @@ int fill_kernel_params(const stan_cuda_data* d, const LaunchIO& io, Workspace* w
 }
 
 int launch_glm(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
+  if (d->family == STAN_CUDA_ORDERED_LOGISTIC && io.ncuts > kMaxCuts) return launch_glm_ordered_wide(d, io, ws, stream);
   if (!d->colblocks.empty()) return launch_glm_colblocks(d, io, ws, stream);  // k > 512
   const Tiling& t = d->t;
   if (d->family == STAN_CUDA_CATEGORICAL_LOGIT && t.layout == kLayoutPlain) return launch_glm_categorical_wide(d, io, ws, stream);

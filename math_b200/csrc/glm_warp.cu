@@ -187,30 +187,13 @@ __device__ __forceinline__ void glm_warp_body(const GlmKernelParams& p) {
       } else if ((p.flags & STAN_CUDA_NEED_DCUTS) && ncuts > 0) {
         // many classes: one owner lane per row adds into this warp's bins, rows in order, so the sum is
         // the same on every run (no floating-point atomics)
-        // Rows of the warp that hit the same bin are found with match.any; every member adds the group's values in
-        // lane order (so the sum does not depend on timing) and the lowest lane of the group makes the one update of
-        // that bin.  Two rounds -- all +d2 terms, then all -d1 terms (:192-200) -- instead of one predicated
-        // read-modify-write per row of the warp (32 serial steps at K = 32: 1e6 x 32 x 64 classes 73.9 -> see profiles).
+        // (warp_bin_add: rows of the warp that hit the same bin are grouped with match.any.)  Two rounds -- all +d2 terms,
+        // then all -d1 terms (:192-200) -- instead of one predicated read-modify-write per row of the warp (32 serial
+        // steps at K = 32: 1e6 x 32 x 64 classes 73.9 -> see profiles).
         double* bins = red + size_t(warp) * cols + kpad + 4;
-        auto bin_add = [&](bool active, int key, double val) {
-          const int mykey = active ? key : -1 - lane;  // inactive lanes form groups of their own
-          const unsigned grp = __match_any_sync(0xffffffffu, mykey);
-          unsigned rem = grp;
-          double acc = 0.0;
-          while (__any_sync(0xffffffffu, rem != 0u)) {
-            const int src = rem ? __ffs(rem) - 1 : lane;
-            const double v = __shfl_sync(0xffffffffu, val, src);
-            if (rem) {
-              acc += v;
-              rem &= rem - 1;
-            }
-          }
-          if (active && lane == __ffs(grp) - 1) bins[key] += acc;
-          __syncwarp();
-        };
         const bool mine = own && valid;
-        bin_add(mine && c != ncuts + 1, c - 1, o.t3);
-        bin_add(mine && c != 1, c - 2, -o.t2);
+        warp_bin_add(bins, lane, mine && c != ncuts + 1, c - 1, o.t3);
+        warp_bin_add(bins, lane, mine && c != 1, c - 2, -o.t2);
       }
     } else if (FAMILY == STAN_CUDA_NEG_BINOMIAL_2_LOG) {
       o = nb_row_epilogue(eta, alpha, yv, sigma_row, log_sigma_row, inv_sigma, p.flags, ROWIO && p.nb_rowfun != 0, ROWIO);
@@ -535,12 +518,13 @@ static int prepare_neg_binomial(const stan_cuda_data* d, const LaunchIO& io, Wor
 
 int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, cudaStream_t stream) {
   const Tiling& t = d->t;
+  const int family = io.family_override >= 0 ? io.family_override : d->family;
   if (d->n <= 0 || t.tiles <= 0) return fail(STAN_CUDA_ERR_ARG, "launch_glm: empty data block");
   const int sms = sm_count(d->device);
   int ctas_per_sm = tuning().ctas_per_sm;
   if (ctas_per_sm <= 0 || ctas_per_sm > 2) ctas_per_sm = 2;
   const size_t budget = (size_t(228) * 1024) / ctas_per_sm - 1024 - 64;
-  const int ncuts = d->family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
+  const int ncuts = family == STAN_CUDA_ORDERED_LOGISTIC ? io.ncuts : 0;
   if (ncuts < 0 || ncuts > kMaxCuts)
     return fail(STAN_CUDA_ERR_ARG, "launch_glm: ordered_logistic supports at most 1024 cut-points on the device");
   const size_t cols = size_t(t.kpad) + 4 + ncuts;
@@ -575,9 +559,9 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   const bool rowio = io.d_alpha_vec || io.d_sigma_vec || io.d_row_dalpha || io.d_row_dsigma;
   // neg_binomial_2_log qualifies on its histogram path (its pre-kernel joins the chain, prepare_neg_binomial);
   // ordered_logistic as it is (class table and bins live in shared memory)
-  const bool nb_hist = d->family == STAN_CUDA_NEG_BINOMIAL_2_LOG && !io.d_sigma_vec && d->hist && !io.d_y;
+  const bool nb_hist = family == STAN_CUDA_NEG_BINOMIAL_2_LOG && !io.d_sigma_vec && d->hist && !io.d_y;
   const bool pdl = pdl_enabled() && !rowio && !io.shared_gpu &&
-                   (d->family <= STAN_CUDA_NORMAL_ID || d->family == STAN_CUDA_ORDERED_LOGISTIC || nb_hist);
+                   (family <= STAN_CUDA_NORMAL_ID || family == STAN_CUDA_ORDERED_LOGISTIC || nb_hist);
   if (pdl && grid64 == int64_t(sms) * ctas_per_sm && grid64 > pdl_slack() + 8) grid64 -= pdl_slack();
   const int grid = int(grid64);
   int group_size = 1;
@@ -595,7 +579,7 @@ int launch_glm_warp(const stan_cuda_data* d, const LaunchIO& io, Workspace* ws, 
   p.ord_private = ord_private_bins(t, ncuts) ? 1 : 0;
   p.pair = pair_mode(t) && stages >= 3 ? 1 : 0;
   p.pdl = pdl ? 1 : 0;
-  switch (d->family) {
+  switch (family) {
     case STAN_CUDA_BERNOULLI_LOGIT:
       return rowio ? launch_warp_inst<STAN_CUDA_BERNOULLI_LOGIT, true>(p, grid, smem, stream)
                    : launch_warp_inst<STAN_CUDA_BERNOULLI_LOGIT, false>(p, grid, smem, stream);

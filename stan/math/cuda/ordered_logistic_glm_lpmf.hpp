@@ -28,7 +28,7 @@ struct ordered_logistic_glm_eligible
  * checks of the cut-points :79-85 unchanged and in the reference's order; check_bounded(y, 1,
  * N_classes) :78 is answered by the device from the range of y computed at cache fill; the lazy
  * finiteness checks :119-122 run on the host only when the device reports a non-finite sum of
- * locations.  The device limit (1024 cut-points) is reported as std::system_error.
+ * locations.  Any number of cut-points (beyond 1024 the device runs its general path, glm_ordered_wide.cu).
  */
 template <bool propto, typename T_beta_scalar, typename T_cuts_scalar>
 return_type_t<T_beta_scalar, T_cuts_scalar> ordered_logistic_glm_lpmf_device(

@@ -277,6 +277,27 @@ TEST(CudaGlmVariants, ordered_logistic) {
   y_low[17] = 0;
   EXPECT_THROW(ordered_logistic_glm_lpmf(y_high, p.x, beta, cuts), std::domain_error);
   EXPECT_THROW(ordered_logistic_glm_lpmf(y_low, p.x, beta, cuts), std::domain_error);
+  stan::math::recover_memory();
+}
+
+TEST(CudaGlmVariants, ordered_logistic_with_more_cut_points_than_the_fused_kernel_holds) {
+  // the reference takes any number of classes (ordered_logistic_glm_lpmf.hpp:69-102); beyond 1024 cut-points the device
+  // evaluates location / rows / gradient as separate passes
+  using stan::math::ordered_logistic_glm_lpmf;
+  using stan::math::ordered_logistic_glm_lpmf_reference_cpu;
+  Problem p = make_problem(4001, 19, 12);
+  const int ncuts = 1500;
+  VectorXd cuts_d(ncuts);
+  for (int j = 0; j < ncuts; ++j) cuts_d[j] = -3.0 + 6.0 * j / ncuts + 0.001 * ((j * 7) % 3);
+  vector_v cuts = to_v(cuts_d);
+  vector_v beta = to_v(p.beta);
+  std::vector<int> y(p.y_pois.size());
+  for (size_t i = 0; i < y.size(); ++i) y[i] = 1 + static_cast<int>((i * 131 + p.y_pois[i]) % (ncuts + 1));
+  STAN_CUDA_PARITY("ordered_logistic, 1500 cut-points", ordered_logistic_glm_lpmf(y, p.x, beta, cuts),
+                   ordered_logistic_glm_lpmf_reference_cpu(y, p.x, beta, cuts), adj(beta), adj(cuts));
+  STAN_CUDA_PARITY("ordered_logistic, 1500 data cut-points", ordered_logistic_glm_lpmf(y, p.x, beta, cuts_d),
+                   ordered_logistic_glm_lpmf_reference_cpu(y, p.x, beta, cuts_d), adj(beta));
+  stan::math::recover_memory();
 }
 
 TEST(CudaGlmVariants, categorical_logit) {

@@ -118,10 +118,39 @@ def test_ordered_logistic_error_contract(glm):
     assert_close(lp, o["lp"], "ordered 301 classes lp")
     assert_close(g["beta"], o["dbeta"], "ordered 301 classes dbeta")
     assert_close(g["cuts"], o["dcuts"], "ordered 301 classes dcuts")
-    # more cut-points than the class table in shared memory holds: loud error, no fallback
-    with pytest.raises(Exception) as e:
-        f([1] * 5, x, beta, np.arange(1100.0))
-    assert "1024" in str(e.value)
+    # more cut-points than the fused kernel's class table holds: the general path, same answer as the reference's loop
+    lp, g = f([1, 1100, 2, 1101, 570], x, beta, np.arange(1100.0) * 0.01)
+    o = L.oracle_ordered_logistic_glm(x, [1, 1100, 2, 1101, 570], beta, np.arange(1100.0) * 0.01)
+    assert_close(lp, o["lp"], "ordered 1101 classes lp")
+    assert_close(g["cuts"], o["dcuts"], "ordered 1101 classes dcuts")
+
+
+# beyond 1024 cut-points the evaluation runs as location / rows / gradient passes with the d/dcuts bins in global memory
+# (glm_ordered_wide.cu); k > 512 adds the column blocks.  The reference has no limit (ordered_logistic_glm_lpmf.hpp:69-102).
+@pytest.mark.parametrize("n,k,ncuts", [(20000, 24, 1024), (20000, 24, 1025), (100003, 16, 2000), (6000, 600, 1500),
+                                        (300, 3, 5000), (50, 1100, 1100), (1, 1, 1025)])
+def test_ordered_logistic_many_cut_points(glm, L, n, k, ncuts):
+    rng = np.random.default_rng(n + k + ncuts)
+    x = np.asfortranarray(rng.standard_normal((n, k)))
+    beta = rng.standard_normal(k) / np.sqrt(k)
+    gap = 8.0 / ncuts
+    cuts = np.linspace(-4.0, 4.0, ncuts) + rng.uniform(0.0, 0.3 * gap, ncuts)   # strictly ascending, gaps >= 0.7 * gap
+    y = (1 + np.searchsorted(cuts, x @ beta + rng.logistic(size=n))).astype(np.int32)
+    y[0] = ncuts + 1 if n > 1 else y[0]   # the open-ended last class
+    if n > 2:
+        y[1] = 1
+    beta = beta + 0.05 * rng.standard_normal(k)
+    flags = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DCUTS
+    ref = L.oracle_ordered_logistic_glm(x, y, beta, cuts)
+    got = glm.ordered_logistic_glm_eval(y, x, beta, cuts, flags)
+    assert got["rc"] == ref["rc"] == 0
+    check_ord_result(got, ref, "ordered %dx%d, %d cut-points" % (n, k, ncuts))
+    again = glm.ordered_logistic_glm_eval(y, x, beta, cuts, flags)
+    assert again["lp"] == got["lp"] and np.array_equal(again["dcuts"], got["dcuts"]) and np.array_equal(again["dbeta"], got["dbeta"])
+    only = glm.ordered_logistic_glm_eval(y, x, beta, cuts, _abi.LP_MAIN | _abi.NEED_DBETA)
+    assert only["lp"] == got["lp"] and np.array_equal(only["dbeta"], got["dbeta"])
+    lp_only = glm.ordered_logistic_glm_eval(y, x, beta, cuts, _abi.LP_MAIN)
+    assert lp_only["lp"] == got["lp"]
 
 
 CAT_FLAGS = _abi.LP_MAIN | _abi.NEED_DBETA | _abi.NEED_DALPHA
