@@ -3,7 +3,7 @@ usage (registers, stack = spills, static shared memory) and the count of the SAS
 made of: UBLKCP (cp.async.bulk, the TMA 1-D copies), SYNCS (mbarrier), DMMA (FP64 tensor-core mma.sync m8n8k4),
 DFMA/DMUL/DADD (FP64 pipe), MUFU (special-function unit), BAR, LDG/STG, RED/ATOM.
 
-    python tools/sass_summary.py > profiles/r01_sass_summary.txt
+    python tools/sass_summary.py > profiles/r02_sass_summary.txt
 """
 import collections
 import os
@@ -22,6 +22,7 @@ def demangle(names):
 
 def short(name):
     name = re.sub(r"^void ", "", name)
+    name = name.replace("(anonymous namespace)::", "")
     name = re.sub(r"\(.*\)$", "", name)
     return name.replace("(anonymous namespace)::", "").replace("stan_cuda::", "")
 
