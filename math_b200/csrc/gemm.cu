@@ -432,17 +432,21 @@ bool direct_copies() {
 
 // One chunk = `nc` pieces of `len` doubles, `host_stride` apart on the host and `dev_stride` apart on the device.
 // Walks the block in chunks that fit a staging buffer; `to_device` selects the direction.  Device -> host returns
-// with the data in place (the stream is synchronised).
+// with the data in place (the stream is synchronised).  max_chunk_cols > 0 caps the columns of a chunk; `gate`, when
+// given, is called in front of the DMA of every chunk with the index one past the chunk's last column (a caller whose
+// columns become final one group after the other makes the stream wait for the group's event there).
 int staged_copy(bool to_device, double* dev, int64_t ld_dev, double* host, int64_t ld_host, int64_t rows, int64_t cols,
-                cudaStream_t stream) {
+                cudaStream_t stream, int64_t max_chunk_cols = 0, const std::function<int(int64_t)>* gate = nullptr) {
   CopyStage* st;
   SC_TRY(copy_stage(&st));
   const int64_t cap = int64_t(st->cap);
   const int64_t piece = std::min(rows, cap);                         // doubles of one column handled at a time
   const int64_t pieces_per_col = (rows + piece - 1) / piece;
-  const int64_t cols_per_chunk = pieces_per_col == 1 ? std::max<int64_t>(1, cap / rows) : 1;
+  int64_t cols_per_chunk = pieces_per_col == 1 ? std::max<int64_t>(1, cap / rows) : 1;
+  if (max_chunk_cols > 0 && cols_per_chunk > max_chunk_cols) cols_per_chunk = max_chunk_cols;
   struct Chunk { int64_t j0, nc, r0, len; int q; };
   auto dma = [&](const Chunk& c) -> int {
+    if (gate) SC_TRY((*gate)(c.j0 + c.nc));
     double* d = dev + c.j0 * ld_dev + c.r0;
     const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
     if (to_device) {
@@ -546,6 +550,16 @@ int copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t ld_de
   return staged_copy(false, d, ld_dev, host, ld_host, rows, cols, stream);
 }
 
+// device -> host in column chunks, each behind its gate (see staged_copy); returns with the data in `host`
+int copy_to_host_gated(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols,
+                       cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate) {
+  if (rows <= 0 || cols <= 0 || direct_copies() || rows * cols <= kDirectCopyDoubles) {
+    SC_TRY(gate(cols));
+    return copy_to_host(host, ld_host, dev, ld_dev, rows, cols, stream);
+  }
+  return staged_copy(false, const_cast<double*>(dev), ld_dev, host, ld_host, rows, cols, stream, chunk_cols, &gate);
+}
+
 int use_device_of(const stan_cuda_matrix* m, ThreadDev** td) {
   SC_TRY(thread_dev(m->device, td));
   SC_CUDA(cudaSetDevice(m->device));
@@ -595,6 +609,10 @@ int dense_copy_to_device(double* dev, int64_t ld_dev, const double* host, int64_
 }
 int dense_copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols, cudaStream_t stream) {
   return copy_to_host(host, ld_host, dev, ld_dev, rows, cols, stream);
+}
+int dense_copy_to_host_gated(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols,
+                             cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate) {
+  return copy_to_host_gated(host, ld_host, dev, ld_dev, rows, cols, stream, chunk_cols, gate);
 }
 
 int matrix_create(int64_t rows, int64_t cols, stan_cuda_matrix** out) {

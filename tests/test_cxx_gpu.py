@@ -25,7 +25,7 @@ BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_po
             "cuda_cholesky_test", "ref_cholesky_decompose_test", "ref_mix_cholesky_decompose_test",
             "cuda_tri_solve_test", "ref_mdivide_left_tri_test", "ref_mdivide_right_tri_test", "ref_mix_mdivide_left_tri_test",
             "cuda_gp_exp_quad_cov_test", "ref_gp_exp_quad_cov_test", "ref_rev_gp_exp_quad_cov_test",
-            "ref_rev_multiply_test", "ref_rev_mdivide_left_tri_test", "ref_mix_mdivide_left_tri_low_test",
+            "ref_mix_mdivide_left_tri_low_test",
             "ref_multi_normal_cholesky_test", "ref_rev_multi_normal_cholesky_test"]
 
 
