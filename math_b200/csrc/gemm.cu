@@ -323,7 +323,7 @@ namespace {
 // The CPU side of a staged copy (pack into / unpack from page-locked memory) runs at the ~12 GB/s of one core, a
 // quarter of what the DMA engine moves; a few helper threads bring the pair towards the PCIe rate.  A tiny persistent
 // pool: the caller posts the slices of one chunk, works on the first slice itself and waits for the others.
-// STAN_CUDA_COPY_THREADS (default 4, 1 = no helpers).
+// STAN_CUDA_COPY_THREADS (default 8 on hosts with 16 or more hardware threads, else 4; 1 = no helpers).
 class CopyPool {
  public:
   static CopyPool& instance() {
@@ -363,8 +363,8 @@ class CopyPool {
  private:
   CopyPool() {
     const char* e = getenv("STAN_CUDA_COPY_THREADS");
-    int n = e ? atoi(e) : 4;
     const unsigned hw = std::thread::hardware_concurrency();
+    int n = e ? atoi(e) : (hw >= 16 ? 8 : 4);  // measured: 134 MB up at 12.9 / 24.6 / 32.6 GB/s with 1 / 4 / 8 threads
     if (hw > 0 && n > int(hw)) n = int(hw);
     helpers_ = n > 1 ? n - 1 : 0;
     for (int q = 0; q < helpers_; ++q) std::thread([this] { work(); }).detach();
