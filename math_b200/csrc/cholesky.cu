@@ -284,7 +284,10 @@ int set_smem_limits() {  // per device (the attribute belongs to the function on
 int dense_copy_to_device(double* dev, int64_t ld_dev, const double* host, int64_t ld_host, int64_t rows, int64_t cols, cudaStream_t stream);
 int dense_copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols, cudaStream_t stream);
 int dense_copy_to_host_gated(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols,
-                             cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate);
+                             cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate, int tri);
+// one triangle of a square block (tri = 1: lower, 2: upper); see gemm.cu
+int dense_copy_to_device_tri(double* dev, int64_t ld_dev, const double* host, int64_t ld_host, int64_t n, cudaStream_t stream, int tri);
+int dense_copy_to_host_tri(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t n, cudaStream_t stream, int tri);
 
 namespace {
 // A second stream and one event per block column for the calling thread: the factor goes back to the host block column
@@ -389,12 +392,12 @@ int cholesky_host(int64_t n, const double* a, int64_t lda, double* l, int64_t ld
       SC_CUDA(cudaStreamWaitEvent(ov.copy, ov.done[size_t((col_end - 1) / kNB)], 0));
       return STAN_CUDA_OK;
     };
-    SC_TRY(dense_copy_to_host_gated(l, ldl, L.p, ld, n, n, ov.copy, chunk_cols, gate));  // synchronises the copy stream
+    SC_TRY(dense_copy_to_host_gated(l, ldl, L.p, ld, n, n, ov.copy, chunk_cols, gate, 1));  // lower triangle; synchronises the copy stream
     SC_CUDA(cudaStreamSynchronize(td->stream));  // the flags; the buffers are released on this stream
   } else {
     SC_TRY(cholesky_device(dev, A.p, L.p, ld, n, reinterpret_cast<int*>(info.p), W.p, td->stream));
     SC_CUDA(cudaMemcpyAsync(td->h_pinned, info.p, sizeof(double), cudaMemcpyDeviceToHost, td->stream));
-    SC_TRY(dense_copy_to_host(l, ldl, L.p, ld, n, n, td->stream));  // synchronises
+    SC_TRY(dense_copy_to_host_tri(l, ldl, L.p, ld, n, td->stream, 1));  // synchronises
   }
   counters().evals.fetch_add(1, std::memory_order_relaxed);
   const int* info_host = reinterpret_cast<const int*>(td->h_pinned);  // [0]: pivot, [1]: symmetry
@@ -423,9 +426,12 @@ int cholesky_adjoint_host(int64_t n, const double* l, int64_t ldl, const double*
   SC_TRY(W.alloc(size_t(nblk) * kNB * kNB, s));
   SC_TRY(Dsym.alloc(kNB * kNB, s));
   SC_TRY(Tmp.alloc(size_t(ld) * kNB, s));
-  SC_TRY(dense_copy_to_device(L.p, ld, l, ldl, n, n, s));
-  SC_TRY(dense_copy_to_device(Lb.p, ld, l_adj, ldadj, n, n, s));
-  counters().bytes_uploaded.fetch_add(2 * uint64_t(n) * uint64_t(n) * sizeof(double));
+  // both operands are lower triangular: only the triangles travel, into cleared buffers
+  SC_CUDA(cudaMemsetAsync(L.p, 0, size_t(ld) * n * sizeof(double), s));
+  SC_CUDA(cudaMemsetAsync(Lb.p, 0, size_t(ld) * n * sizeof(double), s));
+  SC_TRY(dense_copy_to_device_tri(L.p, ld, l, ldl, n, s, 1));
+  SC_TRY(dense_copy_to_device_tri(Lb.p, ld, l_adj, ldadj, n, s, 1));
+  counters().bytes_uploaded.fetch_add(uint64_t(n) * uint64_t(n + 1) * sizeof(double));
   const size_t smem2 = 2 * kNB * kLD * sizeof(double), smem4 = 4 * kNB * kLD * sizeof(double);
   tri_inv_blocks_kernel<<<unsigned(nblk), kThreads, smem2, s>>>(L.p, ld, n, 1, W.p);  // D_b^-1 for every diagonal block
   SC_CUDA(cudaGetLastError());
@@ -456,7 +462,7 @@ int cholesky_adjoint_host(int64_t n, const double* l, int64_t ldl, const double*
   // the strict upper triangle holds scratch of the symmetric updates: the operands are the lower triangle of A only
   zero_strict_upper_kernel<<<dim3(unsigned((n + 255) / 256), unsigned((n + 63) / 64)), 256, 0, s>>>(Lb.p, ld, n);
   SC_CUDA(cudaGetLastError());
-  SC_TRY(dense_copy_to_host(a_adj, lda, Lb.p, ld, n, n, s));
+  SC_TRY(dense_copy_to_host_tri(a_adj, lda, Lb.p, ld, n, s, 1));
   counters().evals.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;
 }
@@ -487,9 +493,10 @@ int tri_solve_host(int lower, int trans, int64_t n, int64_t m, const double* a, 
   SC_TRY(X.alloc(size_t(ld) * m, s));
   SC_TRY(W.alloc(size_t(nblk) * kNB * kNB, s));
   SC_TRY(Tmp.alloc(size_t(kNB) * m, s));
-  SC_TRY(dense_copy_to_device(A.p, ld, a, lda, n, n, s));
+  SC_CUDA(cudaMemsetAsync(A.p, 0, size_t(ld) * n * sizeof(double), s));
+  SC_TRY(dense_copy_to_device_tri(A.p, ld, a, lda, n, s, lower ? 1 : 2));  // the triangle that is read
   SC_TRY(dense_copy_to_device(X.p, ld, b, ldb, n, m, s));
-  counters().bytes_uploaded.fetch_add((uint64_t(n) * uint64_t(n) + uint64_t(n) * uint64_t(m)) * sizeof(double));
+  counters().bytes_uploaded.fetch_add((uint64_t(n) * uint64_t(n + 1) / 2 + uint64_t(n) * uint64_t(m)) * sizeof(double));
   tri_inv_blocks_kernel<<<unsigned(nblk), kThreads, 2 * kNB * kLD * sizeof(double), s>>>(A.p, ld, n, lower, W.p);
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);

@@ -435,8 +435,12 @@ bool direct_copies() {
 // with the data in place (the stream is synchronised).  max_chunk_cols > 0 caps the columns of a chunk; `gate`, when
 // given, is called in front of the DMA of every chunk with the index one past the chunk's last column (a caller whose
 // columns become final one group after the other makes the stream wait for the group's event there).
+// `tri` (square blocks only): 1 = only the lower triangle travels, 2 = only the upper -- per chunk of columns the rows
+// from the chunk's first diagonal element down (lower) or down to its last (upper); towards the host the rest of the
+// columns is filled with zeros, on the device it is left as it is.
 int staged_copy(bool to_device, double* dev, int64_t ld_dev, double* host, int64_t ld_host, int64_t rows, int64_t cols,
-                cudaStream_t stream, int64_t max_chunk_cols = 0, const std::function<int(int64_t)>* gate = nullptr) {
+                cudaStream_t stream, int64_t max_chunk_cols = 0, const std::function<int(int64_t)>* gate = nullptr,
+                int tri = 0) {
   CopyStage* st;
   SC_TRY(copy_stage(&st));
   const int64_t cap = int64_t(st->cap);
@@ -444,6 +448,11 @@ int staged_copy(bool to_device, double* dev, int64_t ld_dev, double* host, int64
   const int64_t pieces_per_col = (rows + piece - 1) / piece;
   int64_t cols_per_chunk = pieces_per_col == 1 ? std::max<int64_t>(1, cap / rows) : 1;
   if (max_chunk_cols > 0 && cols_per_chunk > max_chunk_cols) cols_per_chunk = max_chunk_cols;
+  static const bool tri_enabled = [] {
+    const char* e = getenv("STAN_CUDA_TRI_COPY");  // 0: triangular operands travel whole (A/B)
+    return !e || atoi(e) != 0;
+  }();
+  if (pieces_per_col != 1 || rows != cols || !tri_enabled) tri = 0;
   struct Chunk { int64_t j0, nc, r0, len; int q; };
   auto dma = [&](const Chunk& c) -> int {
     if (gate) SC_TRY((*gate)(c.j0 + c.nc));
@@ -462,8 +471,10 @@ int staged_copy(bool to_device, double* dev, int64_t ld_dev, double* host, int64
   auto cpu_side = [&](const Chunk& c) -> int {  // pack before the DMA (to device) or unpack after it (to host)
     SC_CUDA(cudaEventSynchronize(st->done[c.q]));
     double* stage = st->buf[c.q];
-    const bool big = size_t(c.nc) * size_t(c.len) * sizeof(double) >= (size_t(1) << 20);
-    if (c.nc == 1) {  // one long piece: byte ranges (4 KiB granules) over the copy threads
+    // host bytes this chunk touches (a triangle on its way to the host also fills the rest of its columns with zeros)
+    const size_t touched = size_t(c.nc) * size_t(tri && !to_device ? rows : c.len) * sizeof(double);
+    const bool big = touched >= (size_t(1) << 20);
+    if (c.nc == 1 && !tri) {  // one long piece: byte ranges (4 KiB granules) over the copy threads
       char* h = reinterpret_cast<char*>(host + c.j0 * ld_host + c.r0);
       char* b = reinterpret_cast<char*>(stage);
       const size_t bytes = size_t(c.len) * sizeof(double), granules = (bytes + 4095) / 4096;
@@ -477,10 +488,18 @@ int staged_copy(bool to_device, double* dev, int64_t ld_dev, double* host, int64
     } else {          // whole columns: column ranges over the copy threads
       auto cols_fn = [&](size_t j0, size_t j1) {
         for (size_t j = j0; j < j1; ++j) {
-          double* h = host + (c.j0 + int64_t(j)) * ld_host + c.r0;
+          double* col = host + (c.j0 + int64_t(j)) * ld_host;
+          double* h = col + c.r0;
           double* b = stage + int64_t(j) * c.len;
-          if (to_device) memcpy(b, h, size_t(c.len) * sizeof(double));
-          else memcpy(h, b, size_t(c.len) * sizeof(double));
+          if (to_device) {
+            memcpy(b, h, size_t(c.len) * sizeof(double));
+          } else {
+            memcpy(h, b, size_t(c.len) * sizeof(double));
+            if (tri) {  // the part of the column that did not travel
+              if (c.r0 > 0) memset(col, 0, size_t(c.r0) * sizeof(double));
+              if (c.r0 + c.len < rows) memset(h + c.len, 0, size_t(rows - c.r0 - c.len) * sizeof(double));
+            }
+          }
         }
       };
       if (big) CopyPool::instance().for_slices(size_t(c.nc), cols_fn);
@@ -494,6 +513,12 @@ int staged_copy(bool to_device, double* dev, int64_t ld_dev, double* host, int64
   for (int64_t j0 = 0; j0 < cols; j0 += cols_per_chunk)
     for (int64_t r0 = 0; r0 < rows; r0 += piece) {
       Chunk c{j0, std::min(cols_per_chunk, cols - j0), r0, std::min(piece, rows - r0), q};
+      if (tri == 1) {         // rows from the first column's diagonal element (even start: 16-byte aligned pieces)
+        c.r0 = j0 & ~int64_t(1);
+        c.len = rows - c.r0;
+      } else if (tri == 2) {  // rows down to the last column's diagonal element
+        c.len = std::min(rows, j0 + c.nc);
+      }
       q ^= 1;
       if (to_device) {
         SC_TRY(cpu_side(c));  // waits for the DMA that last read this buffer, then packs
@@ -552,12 +577,25 @@ int copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t ld_de
 
 // device -> host in column chunks, each behind its gate (see staged_copy); returns with the data in `host`
 int copy_to_host_gated(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols,
-                       cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate) {
+                       cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate, int tri) {
   if (rows <= 0 || cols <= 0 || direct_copies() || rows * cols <= kDirectCopyDoubles) {
     SC_TRY(gate(cols));
     return copy_to_host(host, ld_host, dev, ld_dev, rows, cols, stream);
   }
-  return staged_copy(false, const_cast<double*>(dev), ld_dev, host, ld_host, rows, cols, stream, chunk_cols, &gate);
+  return staged_copy(false, const_cast<double*>(dev), ld_dev, host, ld_host, rows, cols, stream, chunk_cols, &gate, tri);
+}
+
+// Square n x n blocks of which one triangle matters (tri = 1: lower, 2: upper): only that triangle crosses the bus.
+// Towards the device the other triangle of `dev` keeps its contents (the callers clear the buffer first); towards the
+// host it is filled with zeros.  Small blocks travel whole (the device copy of the other triangle is then the caller's).
+int copy_to_device_tri(double* dev, int64_t ld_dev, const double* host, int64_t ld_host, int64_t n, cudaStream_t stream, int tri) {
+  if (n <= 0) return STAN_CUDA_OK;
+  if (n * n <= kDirectCopyDoubles || direct_copies()) return copy_to_device(dev, ld_dev, host, ld_host, n, n, stream);
+  return staged_copy(true, dev, ld_dev, const_cast<double*>(host), ld_host, n, n, stream, 0, nullptr, tri);
+}
+int copy_to_host_tri(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t n, cudaStream_t stream, int tri) {
+  if (n <= 0 || n * n <= kDirectCopyDoubles || direct_copies()) return copy_to_host(host, ld_host, dev, ld_dev, n, n, stream);
+  return staged_copy(false, const_cast<double*>(dev), ld_dev, host, ld_host, n, n, stream, 0, nullptr, tri);
 }
 
 int use_device_of(const stan_cuda_matrix* m, ThreadDev** td) {
@@ -611,8 +649,14 @@ int dense_copy_to_host(double* host, int64_t ld_host, const double* dev, int64_t
   return copy_to_host(host, ld_host, dev, ld_dev, rows, cols, stream);
 }
 int dense_copy_to_host_gated(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t rows, int64_t cols,
-                             cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate) {
-  return copy_to_host_gated(host, ld_host, dev, ld_dev, rows, cols, stream, chunk_cols, gate);
+                             cudaStream_t stream, int64_t chunk_cols, const std::function<int(int64_t)>& gate, int tri) {
+  return copy_to_host_gated(host, ld_host, dev, ld_dev, rows, cols, stream, chunk_cols, gate, tri);
+}
+int dense_copy_to_device_tri(double* dev, int64_t ld_dev, const double* host, int64_t ld_host, int64_t n, cudaStream_t stream, int tri) {
+  return copy_to_device_tri(dev, ld_dev, host, ld_host, n, stream, tri);
+}
+int dense_copy_to_host_tri(double* host, int64_t ld_host, const double* dev, int64_t ld_dev, int64_t n, cudaStream_t stream, int tri) {
+  return copy_to_host_tri(host, ld_host, dev, ld_dev, n, stream, tri);
 }
 
 int matrix_create(int64_t rows, int64_t cols, stan_cuda_matrix** out) {
