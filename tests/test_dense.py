@@ -331,6 +331,25 @@ def test_cholesky_full_size_properties(dense):
     assert abs(fd - analytic) <= 1e-6 * max(abs(analytic), 1.0)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [50, 300, 1100])
+def test_cholesky_adjoint_reads_lower_triangles_only(dense, n):
+    """the strict upper triangles of L and of its adjoint are never read (the C++ node hands over work matrices whose
+    upper triangles hold whatever the previous evaluation left there): poisoned with NaN, same result bit for bit.
+    n = 50 travels whole, the others as triangles (staged_copy's tri mode)."""
+    a = _spd(n, 21)
+    l = dense.cholesky_decompose(a)
+    w = np.tril(np.random.default_rng(n).uniform(-1, 1, (n, n)))
+    want = dense.cholesky_adjoint(l, w)
+    upper = np.triu(np.ones((n, n), bool), 1)
+    lp, wp = l.copy(), w.copy()
+    lp[upper] = np.nan
+    wp[upper] = np.nan
+    got = dense.cholesky_adjoint(np.asfortranarray(lp), np.asfortranarray(wp))
+    assert np.array_equal(got, want)
+    assert not np.triu(got, 1).any()
+
+
 # ---- mdivide_left_tri --------------------------------------------------------------------------------------
 @pytest.mark.gpu
 def test_device_tri_solve_matches_golden(dense, golden_mm):
