@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|d3|d4|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -451,7 +451,7 @@ double cholesky_rev_once(const MatrixXd& A, Result* out) {
 }
 
 // vectorised lpmf with an integer outcome and a var vector operand (DENSITY 1: bernoulli_logit_lpmf,
-// 2: poisson_log_lpmf); one evaluation = forward + grad() + reading the N adjoints
+// 2: poisson_log_lpmf, 3: poisson_lpmf, 4: bernoulli_lpmf); one evaluation = forward + grad() + reading the N adjoints
 template <bool GPU, int DENSITY>
 double int_density_once(const std::vector<int>& y, const VectorXd& th_val, Result* out) {
   using namespace stan::math;  // NOLINT
@@ -459,8 +459,10 @@ double int_density_once(const std::vector<int>& y, const VectorXd& th_val, Resul
   vector_v th(th_val.size());
   for (int64_t i = 0; i < th_val.size(); ++i) th[i] = th_val[i];
   const double t0 = now();
-  var lp = DENSITY == 1 ? (GPU ? bernoulli_logit_lpmf(y, th) : bernoulli_logit_lpmf_reference_cpu<false>(y, th))
-                        : (GPU ? poisson_log_lpmf(y, th) : poisson_log_lpmf_reference_cpu<false>(y, th));
+  var lp = DENSITY == 1   ? (GPU ? bernoulli_logit_lpmf(y, th) : bernoulli_logit_lpmf_reference_cpu<false>(y, th))
+           : DENSITY == 2 ? (GPU ? poisson_log_lpmf(y, th) : poisson_log_lpmf_reference_cpu<false>(y, th))
+           : DENSITY == 3 ? (GPU ? poisson_lpmf(y, th) : poisson_lpmf_reference_cpu<false>(y, th))
+                          : (GPU ? bernoulli_lpmf(y, th) : bernoulli_lpmf_reference_cpu<false>(y, th));
   grad(lp.vi_);
   out->lp = lp.val();
   out->grad.resize(th.size());
@@ -659,6 +661,41 @@ int run(int argc, char** argv) {
     Timing tg = time_reps(3, reps, 30, gpu);
     std::printf("\"what\": \"%s N=%lld, n data, operand var vector\", ", bern ? "bernoulli_logit_lpmf" : "poisson_log_lpmf",
                 (long long)n);
+    print_timing("gpu", tg);
+    if (!no_cpu) {
+      Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, cpu);
+      std::printf(", ");
+      print_timing("cpu_reference_1_thread", tc);
+      std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
+    }
+    std::printf(", \"algorithmic_device_bytes\": %lld}\n", (long long)(n * 20));
+    return 0;
+  }
+
+  if (config == "d3" || config == "d4") {  // poisson_lpmf(n | lambda), bernoulli_lpmf(n | theta)
+    const bool pois = config == "d3";
+    const int64_t n = n_override ? n_override : 1000000;
+    std::vector<int> y(n);
+    VectorXd op(n);
+    Rng r(pois ? 1013 : 1014);
+    for (int64_t i = 0; i < n; ++i) {
+      const double z = r.normal();
+      if (pois) {
+        op[i] = std::exp(0.5 + z);
+        y[i] = int(std::max(0.0, std::floor(op[i] + r.normal())));
+        op[i] *= std::exp(0.1 * r.normal());
+      } else {
+        op[i] = 1.0 / (1.0 + std::exp(-2.0 * z));
+        y[i] = r.normal() < 2.0 * z ? 1 : 0;
+        op[i] = std::min(std::max(op[i], 1e-6), 1.0 - 1e-6);
+      }
+    }
+    Result g, c;
+    auto gpu = [&] { return pois ? int_density_once<true, 3>(y, op, &g) : int_density_once<true, 4>(y, op, &g); };
+    auto cpu = [&] { return pois ? int_density_once<false, 3>(y, op, &c) : int_density_once<false, 4>(y, op, &c); };
+    gpu();
+    Timing tg = time_reps(3, reps, 30, gpu);
+    std::printf("\"what\": \"%s N=%lld, n data, operand var vector\", ", pois ? "poisson_lpmf" : "bernoulli_lpmf", (long long)n);
     print_timing("gpu", tg);
     if (!no_cpu) {
       Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, cpu);

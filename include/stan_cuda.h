@@ -187,6 +187,8 @@ typedef struct stan_cuda_normal_args {
  * per-element terms are the epilogues of the GLM kernels). */
 #define STAN_CUDA_DENSITY_BERNOULLI_LOGIT 1 /* bernoulli_logit_lpmf(n | theta)  prim/scal/prob/bernoulli_logit_lpmf.hpp:28-89 */
 #define STAN_CUDA_DENSITY_POISSON_LOG 2     /* poisson_log_lpmf(n | alpha)      prim/scal/prob/poisson_log_lpmf.hpp:22-97 */
+#define STAN_CUDA_DENSITY_POISSON 3         /* poisson_lpmf(n | lambda)         prim/scal/prob/poisson_lpmf.hpp:20-77 */
+#define STAN_CUDA_DENSITY_BERNOULLI 4       /* bernoulli_lpmf(n | theta)        prim/scal/prob/bernoulli_lpmf.hpp:28-112 */
 
 typedef struct stan_cuda_density_args {
   int32_t density;      /* STAN_CUDA_DENSITY_* */
@@ -194,7 +196,7 @@ typedef struct stan_cuda_density_args {
   int64_t n;            /* max_size(y, theta) */
   const int32_t* y;     /* host; integer outcomes: immutable data, cached on the device when y_len == n */
   int64_t y_len;        /* 1 or n */
-  const double* theta;  /* host; logit (bernoulli_logit) or log rate (poisson_log) */
+  const double* theta;  /* host; logit (bernoulli_logit), log rate (poisson_log), rate (poisson) or probability (bernoulli) */
   int64_t theta_len;    /* 1 or n */
   double* lp;           /* [1] */
   double* dtheta;       /* [theta_len]: per element, or the sum over n for a scalar operand */
@@ -311,7 +313,8 @@ STAN_CUDA_API int stan_cuda_glm_eval_batch(const stan_cuda_glm_args* items, int 
 STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
 /* Returns STAN_CUDA_BAD_OPERAND when an outcome is outside the density's support (bernoulli_logit: not in
  * {0, 1}, bernoulli_logit_lpmf.hpp:42; poisson_log: negative, poisson_log_lpmf.hpp:38) or the operand is NaN
- * (:43 / :39) -- every element is tested inside the kernel, the wrapper then runs the reference's own checks
+ * (:43 / :39; poisson: NaN or negative rate, poisson_lpmf.hpp:32-33; bernoulli: probability not finite or outside
+ * [0, 1], bernoulli_lpmf.hpp:42-43) -- every element is tested inside the kernel, the wrapper then runs the reference's own checks
  * to throw the identical exception -- and STAN_CUDA_LOG_ZERO as described above. */
 STAN_CUDA_API int stan_cuda_density_eval(const stan_cuda_density_args* a);
 /* Returns STAN_CUDA_BAD_OPERAND when y is NaN, nu or sigma is not positive and finite, or mu is not finite

@@ -116,8 +116,9 @@ class MultiplyArgs(C.Structure):
     ]
 
 
-DENSITY_BERNOULLI_LOGIT, DENSITY_POISSON_LOG = 1, 2
-DENSITIES = {"bernoulli_logit": DENSITY_BERNOULLI_LOGIT, "poisson_log": DENSITY_POISSON_LOG}
+DENSITY_BERNOULLI_LOGIT, DENSITY_POISSON_LOG, DENSITY_POISSON, DENSITY_BERNOULLI = 1, 2, 3, 4
+DENSITIES = {"bernoulli_logit": DENSITY_BERNOULLI_LOGIT, "poisson_log": DENSITY_POISSON_LOG, "poisson": DENSITY_POISSON,
+             "bernoulli": DENSITY_BERNOULLI}
 
 
 class DensityArgs(C.Structure):

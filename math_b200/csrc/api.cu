@@ -1076,7 +1076,7 @@ static int get_ivec_entry(const int32_t* v, int64_t n, int device, int want_lgam
 int density_eval(const stan_cuda_density_args* a) {
   NvtxRange range("stan_cuda_density_eval");
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: null args");
-  if (a->density != STAN_CUDA_DENSITY_BERNOULLI_LOGIT && a->density != STAN_CUDA_DENSITY_POISSON_LOG)
+  if (a->density < STAN_CUDA_DENSITY_BERNOULLI_LOGIT || a->density > STAN_CUDA_DENSITY_BERNOULLI)
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: unknown density");
   if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_density_eval: negative n");
   if (a->n == 0) {  // size_zero(n, theta) -> 0 (bernoulli_logit_lpmf.hpp:36-38, poisson_log_lpmf.hpp:32-34)
@@ -1096,7 +1096,7 @@ int density_eval(const stan_cuda_density_args* a) {
   const bool yv = a->y_len != 1, tv = a->theta_len != 1;
   const bool need_d = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dtheta;
   std::shared_ptr<Entry> ycache;
-  const bool poisson = a->density == STAN_CUDA_DENSITY_POISSON_LOG;
+  const bool poisson = a->density == STAN_CUDA_DENSITY_POISSON_LOG || a->density == STAN_CUDA_DENSITY_POISSON;
   if (yv) SC_TRY(get_ivec_entry(a->y, n, dev, poisson ? 1 : 0, td->stream, &ycache));
   const size_t nal = (size_t(n) + 1) & ~size_t(1);
   size_t need = 8;
@@ -1136,6 +1136,27 @@ int density_eval(const stan_cuda_density_args* a) {
   if (bits & 4u) {
     if (a->lp) *a->lp = -INFINITY;
     return STAN_CUDA_LOG_ZERO;
+  }
+  if (a->density == STAN_CUDA_DENSITY_BERNOULLI && !tv) {
+    // scalar probability: the reference's closed form from the number of successes (bernoulli_lpmf.hpp:63-91; the
+    // two one-sided branches avoid 0 * log(0)); the kernel counted them (exact in a double)
+    const double N = double(n), ones = res[1], th = a->theta[0];
+    double lp = 0.0, d = 0.0;
+    if (ones == N) {
+      lp = N * log(th);
+      d = N / th;
+    } else if (ones == 0.0) {
+      lp = N * log1p(-th);
+      d = N / (th - 1.0);
+    } else {
+      lp = ones * log(th);
+      lp += (N - ones) * log1p(-th);
+      d = ones / th;
+      d += (N - ones) / (th - 1.0);
+    }
+    if (a->lp) *a->lp = (a->flags & STAN_CUDA_LP_MAIN) ? lp : 0.0;
+    if (need_d) a->dtheta[0] = d;
+    return STAN_CUDA_OK;
   }
   if (a->lp) *a->lp = res[0];
   if (need_d && !tv) a->dtheta[0] = res[1];

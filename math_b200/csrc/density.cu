@@ -3,6 +3,8 @@
 // with the linear predictor given directly:
 //   bernoulli_logit_lpmf(n | theta)   stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
 //   poisson_log_lpmf(n | alpha)       stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93
+//   poisson_lpmf(n | lambda)          stan/math/prim/scal/prob/poisson_lpmf.hpp:45-71
+//   bernoulli_lpmf(n | theta)         stan/math/prim/scal/prob/bernoulli_lpmf.hpp:54-107
 // Same shape as normal_lpdf.cu: grid-stride map, fixed-order reduction (warp shuffle tree -> warps in order ->
 // CTAs in order by the last CTA), each operand a device vector or a scalar passed by value, per-element
 // partials written only for a vector operand (a scalar operand gets the sum: what the reference accumulates
@@ -42,6 +44,26 @@ __global__ void __launch_bounds__(THREADS) density_kernel(const DensityKernelPar
       lp = ntheta > 20.0 ? -e : (ntheta < -20.0 ? ntheta : -log1p(e));
       d = ntheta > 20.0 ? -e : (ntheta < -20.0 ? sign : sign * e / (e + 1.0));
       if (!lp_main) lp = 0.0;
+    } else if (DENSITY == STAN_CUDA_DENSITY_BERNOULLI) {
+      bits |= (y < 0 || y > 1) ? 1u : 0u;                                      // :41 check_bounded(n, 0, 1)
+      bits |= (!(fabs(th) <= 1.79769313486231570815e308) || th < 0.0 || th > 1.0) ? 2u : 0u;  // :42-43 finite, in [0, 1]
+      if (io.theta_vec) {                                                      // :92-107
+        lp = y == 1 ? log(th) : log1p(-th);
+        d = y == 1 ? 1.0 / th : 1.0 / (th - 1.0);
+        if (!lp_main) lp = 0.0;
+      } else {
+        d = double(y);  // scalar probability: only the number of successes is needed (:63-91; closed form on the host, api.cu)
+      }
+    } else if (DENSITY == STAN_CUDA_DENSITY_POISSON) {
+      bits |= (y < 0) ? 1u : 0u;                                               // :31 check_nonnegative(n)
+      bits |= (th < 0.0) ? 2u : 0u;                                            // :33 check_nonnegative(lambda) (NaN: above)
+      bits |= (th == inf || (th == 0.0 && y != 0)) ? 4u : 0u;                  // :45-54 LOG_ZERO
+      const double yd = double(y);
+      if (!(th == 0.0 && y == 0)) {                                            // :58-66
+        if (lp_const && !io.lgamma_cached) lp -= lgamma(yd + 1.0);
+        if (lp_main) lp += (y == 0 ? 0.0 : yd * log(th)) - th;                 // multiply_log(n, lambda) - lambda
+      }
+      d = yd / th - 1.0;                                                       // :69-70
     } else {
       bits |= (y < 0) ? 1u : 0u;                                               // :38 check_nonnegative(n)
       // :51-62: +inf anywhere, or -inf next to a non-zero count -> the whole density is LOG_ZERO
@@ -98,7 +120,9 @@ __global__ void __launch_bounds__(THREADS) density_kernel(const DensityKernelPar
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
     if (lane == 0) {
-      if (warp == 0 && DENSITY == STAN_CUDA_DENSITY_POISSON_LOG && lp_const && io.lgamma_cached) s -= io.lgamma_total;
+      if (warp == 0 && (DENSITY == STAN_CUDA_DENSITY_POISSON_LOG || DENSITY == STAN_CUDA_DENSITY_POISSON) && lp_const &&
+          io.lgamma_cached)
+        s -= io.lgamma_total;
       io.result[warp] = s;
       if (warp == 0) {
         io.result[2] = 0.0;
@@ -129,6 +153,12 @@ int launch_density(const DensityIO& io, Workspace* ws, int device, cudaStream_t 
       break;
     case STAN_CUDA_DENSITY_POISSON_LOG:
       density_kernel<STAN_CUDA_DENSITY_POISSON_LOG, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_DENSITY_POISSON:
+      density_kernel<STAN_CUDA_DENSITY_POISSON, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_DENSITY_BERNOULLI:
+      density_kernel<STAN_CUDA_DENSITY_BERNOULLI, THREADS><<<grid, THREADS, 0, stream>>>(p);
       break;
     default:
       return fail(STAN_CUDA_ERR_ARG, "launch_density: unknown density");

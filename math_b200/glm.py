@@ -568,7 +568,8 @@ def density_eval(density, n, theta, flags):
     return {"rc": rc, "lp": float(lp[0]), "dtheta": dth[:theta.size].copy()}
 
 
-def _density(function, density, n, theta, propto, theta_var, n_check, n_error, theta_name):
+def _density(function, density, n, theta, propto, theta_var, n_check, n_error, theta_name, theta_check=None,
+             theta_error=None):
     """Call sequence of the reference (bernoulli_logit_lpmf.hpp:36-49, poisson_log_lpmf.hpp:32-49): size_zero -> 0,
     domain errors before the size error, nothing to compute under propto with a constant operand -> 0."""
     nn = np.atleast_1d(np.asarray(n))
@@ -583,6 +584,8 @@ def _density(function, density, n, theta, propto, theta_var, n_check, n_error, t
             raise n_error
         if np.any(np.isnan(th)):
             raise DomainError("%s: %s is nan, but must not be nan!" % (function, theta_name))
+        if theta_check is not None and not theta_check(th):
+            raise theta_error
         if not sizes_ok:
             raise ValueError("%s: Random variable has dimension = %d, expecting dimension = %d" % (function, nn.size, size))
         return 0.0, {"theta": np.zeros(th.size)}
@@ -593,6 +596,8 @@ def _density(function, density, n, theta, propto, theta_var, n_check, n_error, t
     if r["rc"] == _abi.BAD_OPERAND:  # the kernel saw a bad element: the reference's checks name it
         if not n_check(nn):
             raise n_error
+        if theta_check is not None and not np.any(np.isnan(th)):
+            raise theta_error
         raise DomainError("%s: %s is nan, but must not be nan!" % (function, theta_name))
     if r["rc"] == _abi.LOG_ZERO:     # poisson_log_lpmf.hpp:51-62: LOG_ZERO, no partials
         return -np.inf, {"theta": np.zeros(th.size)}
@@ -611,6 +616,23 @@ def poisson_log_lpmf(n, alpha, propto=False, alpha_var=True):
     f = "poisson_log_lpmf"
     return _density(f, "poisson_log", n, alpha, propto, alpha_var, lambda v: bool(np.all(v >= 0)),
                     DomainError("%s: Random variable must be >= 0!" % f), "Log rate parameter")
+
+
+def poisson_lpmf(n, lam, propto=False, lambda_var=True):
+    """stan/math/prim/scal/prob/poisson_lpmf.hpp:20-21; grads: theta (the rate lambda)."""
+    f = "poisson_lpmf"
+    return _density(f, "poisson", n, lam, propto, lambda_var, lambda v: bool(np.all(v >= 0)),
+                    DomainError("%s: Random variable must be >= 0!" % f), "Rate parameter",
+                    lambda t: bool(np.all(t >= 0)), DomainError("%s: Rate parameter must be >= 0!" % f))
+
+
+def bernoulli_lpmf(n, theta, propto=False, theta_var=True):
+    """stan/math/prim/scal/prob/bernoulli_lpmf.hpp:28-29; grads: theta (the chance of success)."""
+    f = "bernoulli_lpmf"
+    return _density(f, "bernoulli", n, theta, propto, theta_var, lambda v: bool(np.all((v >= 0) & (v <= 1))),
+                    DomainError("%s: n must be in the interval [0, 1]" % f), "Probability parameter",
+                    lambda t: bool(np.all(np.isfinite(t) & (t >= 0) & (t <= 1))),
+                    DomainError("%s: Probability parameter must be finite and in the interval [0, 1]" % f))
 
 
 class GlmCall:

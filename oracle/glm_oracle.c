@@ -544,10 +544,94 @@ int oracle_gp_exp_quad_cov(int64_t n1, int64_t n2, int64_t dim, const double* x1
 /* Vectorised elementwise densities with an integer outcome.
  *   bernoulli_logit_lpmf  stan/math/prim/scal/prob/bernoulli_logit_lpmf.hpp:51-80
  *   poisson_log_lpmf      stan/math/prim/scal/prob/poisson_log_lpmf.hpp:51-93
+ *   poisson_lpmf          stan/math/prim/scal/prob/poisson_lpmf.hpp:20-77   (oracle_density_poisson below)
+ *   bernoulli_lpmf        stan/math/prim/scal/prob/bernoulli_lpmf.hpp:28-112 (oracle_density_bernoulli below)
  * Return codes as the product's: BAD_OPERAND where the reference's eager checks throw (:42-43 / :38-39),
  * LOG_ZERO where poisson_log_lpmf returns LOG_ZERO before building partials (:51-62). */
+/* poisson_lpmf(n | lambda), stan/math/prim/scal/prob/poisson_lpmf.hpp:20-77 */
+static int oracle_density_poisson(const stan_cuda_density_args* a) {
+  const int ym = a->y_len != 1, tm = a->theta_len != 1;
+  const int need_d = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dtheta;
+  for (int64_t i = 0; i < a->y_len; ++i)
+    if (a->y[i] < 0) return STAN_CUDA_BAD_OPERAND;                                  /* :31 */
+  for (int64_t i = 0; i < a->theta_len; ++i)
+    if (isnan(a->theta[i]) || a->theta[i] < 0) return STAN_CUDA_BAD_OPERAND;        /* :32-33 */
+  for (int64_t i = 0; i < a->n; ++i)
+    if (isinf(a->theta[tm ? i : 0])) {                                              /* :45-49 */
+      if (a->lp) *a->lp = -INFINITY;
+      return STAN_CUDA_LOG_ZERO;
+    }
+  for (int64_t i = 0; i < a->n; ++i)
+    if (a->theta[tm ? i : 0] == 0 && a->y[ym ? i : 0] != 0) {                       /* :50-54 */
+      if (a->lp) *a->lp = -INFINITY;
+      return STAN_CUDA_LOG_ZERO;
+    }
+  double logp = 0.0;
+  if (need_d) for (int64_t i = 0; i < a->theta_len; ++i) a->dtheta[i] = 0.0;
+  for (int64_t i = 0; i < a->n; ++i) {
+    const int y = a->y[ym ? i : 0];
+    const double lam = a->theta[tm ? i : 0];
+    if (!(lam == 0 && y == 0)) {                                                    /* :59 */
+      if (a->flags & STAN_CUDA_LP_CONST) logp -= lgamma(y + 1.0);                   /* :60-62 */
+      if (a->flags & STAN_CUDA_LP_MAIN)                                             /* :63-66; multiply_log(0, 0) = 0 */
+        logp += ((y == 0 && lam == 0) ? 0.0 : y * log(lam)) - lam;
+    }
+    if (need_d) a->dtheta[tm ? i : 0] += y / lam - 1.0;                             /* :69-72 */
+  }
+  if (a->lp) *a->lp = logp;
+  return STAN_CUDA_OK;
+}
+
+/* bernoulli_lpmf(n | theta), stan/math/prim/scal/prob/bernoulli_lpmf.hpp:28-112 */
+static int oracle_density_bernoulli(const stan_cuda_density_args* a) {
+  const int ym = a->y_len != 1, tm = a->theta_len != 1;
+  const int need_d = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dtheta;
+  const int main_term = (a->flags & STAN_CUDA_LP_MAIN) != 0;
+  for (int64_t i = 0; i < a->y_len; ++i)
+    if (a->y[i] < 0 || a->y[i] > 1) return STAN_CUDA_BAD_OPERAND;                   /* :41 */
+  for (int64_t i = 0; i < a->theta_len; ++i)
+    if (!isfinite(a->theta[i]) || a->theta[i] < 0.0 || a->theta[i] > 1.0) return STAN_CUDA_BAD_OPERAND;  /* :42-43 */
+  double logp = 0.0;
+  if (need_d) for (int64_t i = 0; i < a->theta_len; ++i) a->dtheta[i] = 0.0;
+  if (!tm) {                                                                        /* :58-91 */
+    int64_t sum = 0;
+    for (int64_t i = 0; i < a->n; ++i) sum += a->y[ym ? i : 0];
+    const double th = a->theta[0], N = (double)a->n;
+    double d = 0.0;
+    if (sum == a->n) {
+      logp += N * log(th);
+      d += N / th;
+    } else if (sum == 0) {
+      logp += N * log1p(-th);
+      d += N / (th - 1);
+    } else {
+      logp += sum * log(th);
+      logp += (a->n - sum) * log1p(-th);
+      d += sum / th;
+      d += (a->n - sum) / (th - 1);
+    }
+    if (need_d) a->dtheta[0] = d;
+  } else {                                                                          /* :92-107 */
+    for (int64_t i = 0; i < a->n; ++i) {
+      const int y = a->y[ym ? i : 0];
+      const double th = a->theta[i];
+      logp += y == 1 ? log(th) : log1p(-th);
+      if (need_d) a->dtheta[i] += y == 1 ? 1.0 / th : 1.0 / (th - 1);
+    }
+  }
+  if (a->lp) *a->lp = main_term ? logp : 0.0;
+  return STAN_CUDA_OK;
+}
+
 int oracle_density_eval(const stan_cuda_density_args* a) {
   if (!a || a->n < 0) return STAN_CUDA_ERR_ARG;
+  if (a->density == STAN_CUDA_DENSITY_POISSON || a->density == STAN_CUDA_DENSITY_BERNOULLI) {
+    if (a->n == 0) {
+      if (a->lp) *a->lp = 0.0;
+      return STAN_CUDA_OK;
+    }
+    return a->density == STAN_CUDA_DENSITY_POISSON ? oracle_density_poisson(a) : oracle_density_bernoulli(a);
+  }
   const int ym = a->y_len != 1, tm = a->theta_len != 1;
   const int need_d = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dtheta;
   const int bern = a->density == STAN_CUDA_DENSITY_BERNOULLI_LOGIT;

@@ -296,7 +296,7 @@ int stanref_normal_lpdf(int propto, long n, const double* y, const double* mu,
       err, errlen);
 }
 
-// Vectorised bernoulli_logit_lpmf (density 1) / poisson_log_lpmf (density 2): n int data (n_len 1 or n),
+// Vectorised bernoulli_logit_lpmf (density 1) / poisson_log_lpmf (2) / poisson_lpmf (3) / bernoulli_lpmf (4): n int data (n_len 1 or n),
 // theta a var vector (theta_len n) or var scalar; theta_is_var == 0 evaluates the all-double form (value only).
 int stanref_density(int density, int propto, long n, const int* y, long y_len, const double* theta,
                     long theta_len, int theta_is_var, double* lp, double* dtheta, double* seconds,
@@ -312,6 +312,10 @@ int stanref_density(int density, int propto, long n, const int* y, long y_len, c
 #define STANREF_DCALL(F, P) (ym ? (tm ? F<P>(yv, th) : F<P>(yv, th[0])) : (tm ? F<P>(yv[0], th) : F<P>(yv[0], th[0])))
           if (density == 1)
             r = propto ? STANREF_DCALL(stan::math::bernoulli_logit_lpmf, true) : STANREF_DCALL(stan::math::bernoulli_logit_lpmf, false);
+          else if (density == 3)
+            r = propto ? STANREF_DCALL(stan::math::poisson_lpmf, true) : STANREF_DCALL(stan::math::poisson_lpmf, false);
+          else if (density == 4)
+            r = propto ? STANREF_DCALL(stan::math::bernoulli_lpmf, true) : STANREF_DCALL(stan::math::bernoulli_lpmf, false);
           else
             r = propto ? STANREF_DCALL(stan::math::poisson_log_lpmf, true) : STANREF_DCALL(stan::math::poisson_log_lpmf, false);
           if (lp) *lp = r;
@@ -323,6 +327,10 @@ int stanref_density(int density, int propto, long n, const int* y, long y_len, c
 #define STANREF_DVCALL(F, P) (ym ? (tm ? F<P>(yv, th) : F<P>(yv, t0v)) : (tm ? F<P>(yv[0], th) : F<P>(yv[0], t0v)))
         if (density == 1)
           res = propto ? STANREF_DVCALL(stan::math::bernoulli_logit_lpmf, true) : STANREF_DVCALL(stan::math::bernoulli_logit_lpmf, false);
+        else if (density == 3)
+          res = propto ? STANREF_DVCALL(stan::math::poisson_lpmf, true) : STANREF_DVCALL(stan::math::poisson_lpmf, false);
+        else if (density == 4)
+          res = propto ? STANREF_DVCALL(stan::math::bernoulli_lpmf, true) : STANREF_DVCALL(stan::math::bernoulli_lpmf, false);
         else
           res = propto ? STANREF_DVCALL(stan::math::poisson_log_lpmf, true) : STANREF_DVCALL(stan::math::poisson_log_lpmf, false);
 #undef STANREF_DCALL

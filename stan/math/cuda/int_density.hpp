@@ -8,6 +8,7 @@
 #include <stan/math/cuda/normal_lpdf.hpp>
 #include <stan/math/prim/scal/err/check_bounded.hpp>
 #include <stan/math/prim/scal/err/check_consistent_sizes.hpp>
+#include <stan/math/prim/scal/err/check_finite.hpp>
 #include <stan/math/prim/scal/err/check_nonnegative.hpp>
 #include <stan/math/prim/scal/err/check_not_nan.hpp>
 #include <stan/math/prim/scal/fun/constants.hpp>
@@ -140,6 +141,80 @@ return_type_t<T_log_rate> poisson_log_lpmf_device(const T_n& n, const T_log_rate
   }
   if (rc == STAN_CUDA_LOG_ZERO) {
     return LOG_ZERO;
+  }
+  return ops_partials.build(logp);
+}
+
+/**
+ * GPU body of poisson_lpmf (reference: stan/math/prim/scal/prob/poisson_lpmf.hpp:20-77): the loop :57-73 becomes one
+ * kernel, which also answers the eager checks :31-33 (STAN_CUDA_BAD_OPERAND) and the two LOG_ZERO scans :45-54
+ * (STAN_CUDA_LOG_ZERO).  A zero rate next to a zero count contributes no term (:59) and the partial 0/0 - 1, as there.
+ */
+template <bool propto, typename T_n, typename T_rate>
+return_type_t<T_rate> poisson_lpmf_device(const T_n& n, const T_rate& lambda) {
+  static const char* function = "poisson_lpmf";
+  if (size_zero(n, lambda)) {
+    return 0.0;
+  }
+  const size_t N = max_size(n, lambda);
+  const bool sizes_ok = (!is_vector<T_n>::value || length(n) == N) && length(lambda) == N;
+  if (!sizes_ok || !include_summand<propto, T_rate>::value) {
+    check_nonnegative(function, "Random variable", n);
+    check_not_nan(function, "Rate parameter", lambda);
+    check_nonnegative(function, "Rate parameter", lambda);
+    check_consistent_sizes(function, "Random variable", n, "Rate parameter", lambda);
+    return 0.0;
+  }
+  double* const stage = int_density_stage(lambda);
+  double* const sinks[5] = {gathered_by_node<T_rate>::value ? stage : nullptr, nullptr, nullptr, nullptr, nullptr};
+  arena_partials<T_rate> ops_partials(lambda, double(), double(), double(), double(), sinks);
+  double logp = 0;
+  const int rc = int_density_call(STAN_CUDA_DENSITY_POISSON, include_summand<propto>::value, n, lambda, N, ops_partials,
+                                  stage, &logp);
+  check_cuda_rc(function, rc);
+  if (rc == STAN_CUDA_BAD_OPERAND) {
+    check_nonnegative(function, "Random variable", n);
+    check_not_nan(function, "Rate parameter", lambda);
+    check_nonnegative(function, "Rate parameter", lambda);
+    throw std::domain_error(std::string(function) + ": operand outside the domain (device check)");
+  }
+  if (rc == STAN_CUDA_LOG_ZERO) {
+    return LOG_ZERO;
+  }
+  return ops_partials.build(logp);
+}
+
+/**
+ * GPU body of bernoulli_lpmf (reference: stan/math/prim/scal/prob/bernoulli_lpmf.hpp:28-112): the per-element loop
+ * :92-107 becomes one kernel, which also answers the eager checks :41-43; a probability container of length one takes
+ * the reference's closed form from the number of successes (:58-91) inside the library.
+ */
+template <bool propto, typename T_n, typename T_prob>
+return_type_t<T_prob> bernoulli_lpmf_device(const T_n& n, const T_prob& theta) {
+  static const char* function = "bernoulli_lpmf";
+  if (size_zero(n, theta)) {
+    return 0.0;
+  }
+  const size_t N = max_size(n, theta);
+  const bool sizes_ok = (!is_vector<T_n>::value || length(n) == N) && length(theta) == N;
+  if (!sizes_ok || !include_summand<propto, T_prob>::value) {
+    check_bounded(function, "n", n, 0, 1);
+    check_finite(function, "Probability parameter", theta);
+    check_bounded(function, "Probability parameter", theta, 0.0, 1.0);
+    check_consistent_sizes(function, "Random variable", n, "Probability parameter", theta);
+    return 0.0;
+  }
+  double* const stage = int_density_stage(theta);
+  double* const sinks[5] = {gathered_by_node<T_prob>::value ? stage : nullptr, nullptr, nullptr, nullptr, nullptr};
+  arena_partials<T_prob> ops_partials(theta, double(), double(), double(), double(), sinks);
+  double logp = 0;
+  const int rc = int_density_call(STAN_CUDA_DENSITY_BERNOULLI, false, n, theta, N, ops_partials, stage, &logp);
+  check_cuda_rc(function, rc);
+  if (rc == STAN_CUDA_BAD_OPERAND) {
+    check_bounded(function, "n", n, 0, 1);
+    check_finite(function, "Probability parameter", theta);
+    check_bounded(function, "Probability parameter", theta, 0.0, 1.0);
+    throw std::domain_error(std::string(function) + ": operand outside the domain (device check)");
   }
   return ops_partials.build(logp);
 }

@@ -618,6 +618,124 @@ TEST(CudaIntDensity, same_exceptions_and_log_zero_as_the_reference) {
   stan::math::recover_memory();
 }
 
+TEST(CudaIntDensity, poisson_and_bernoulli_match_reference_loop) {
+  const int n = 100000;
+  Problem p = make_problem(n, 1, 10);
+  VectorXd lam_d(n), th_d(n);
+  for (int i = 0; i < n; ++i) {
+    lam_d[i] = 0.05 + std::exp(0.7 * p.y_norm[i]);                    // rates
+    th_d[i] = 1.0 / (1.0 + std::exp(-1.5 * p.y_norm[i]));             // probabilities
+    th_d[i] = std::min(std::max(th_d[i], 1e-6), 1.0 - 1e-6);
+  }
+  lam_d[5] = 1e-300;  // the corners
+  lam_d[6] = 1e6;
+  th_d[5] = 1e-300;
+  th_d[6] = 1.0 - 1e-16;
+  std::vector<int> y_pois = p.y_pois, y_bern = p.y_bern;
+  y_pois[5] = 0;
+  y_bern[5] = 0;
+  y_bern[6] = 1;
+  vector_v lambda = to_v(lam_d), theta = to_v(th_d);
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("poisson_lpmf", poisson_lpmf(y_pois, lambda), poisson_lpmf_reference_cpu<false>(y_pois, lambda), adj(lambda));
+  STAN_CUDA_PARITY("poisson_lpmf propto", poisson_lpmf<true>(y_pois, lambda),
+                   poisson_lpmf_reference_cpu<true>(y_pois, lambda), adj(lambda));
+  STAN_CUDA_PARITY("poisson_lpmf scalar n", poisson_lpmf(2, lambda), poisson_lpmf_reference_cpu<false>(2, lambda), adj(lambda));
+  STAN_CUDA_PARITY("bernoulli_lpmf", bernoulli_lpmf(y_bern, theta), bernoulli_lpmf_reference_cpu<false>(y_bern, theta), adj(theta));
+  STAN_CUDA_PARITY("bernoulli_lpmf propto", bernoulli_lpmf<true>(y_bern, theta),
+                   bernoulli_lpmf_reference_cpu<true>(y_bern, theta), adj(theta));
+  STAN_CUDA_PARITY("bernoulli_lpmf scalar n", bernoulli_lpmf(1, theta), bernoulli_lpmf_reference_cpu<false>(1, theta), adj(theta));
+  // the deprecated aliases forward to the routed functions (prim/scal/prob/poisson_log.hpp, bernoulli_log.hpp)
+  STAN_CUDA_PARITY("poisson_log alias", poisson_log(y_pois, lambda), poisson_lpmf_reference_cpu<false>(y_pois, lambda), adj(lambda));
+  // double operands: value only, double return type
+  const double v = poisson_lpmf(y_pois, lam_d);
+  expect_rel(v, poisson_lpmf_reference_cpu<false>(y_pois, lam_d), std::fabs(v), "double lambda");
+  const double w = bernoulli_lpmf(y_bern, th_d);
+  expect_rel(w, bernoulli_lpmf_reference_cpu<false>(y_bern, th_d), std::fabs(w), "double theta");
+  EXPECT_EQ(0.0, poisson_lpmf<true>(y_pois, lam_d));  // propto with a constant operand
+  // a container of length one takes bernoulli_lpmf's closed form (:58-91)
+  vector_v one = to_v(VectorXd::Constant(1, 0.3));
+  STAN_CUDA_PARITY("bernoulli_lpmf, one probability", bernoulli_lpmf(1, one), bernoulli_lpmf_reference_cpu<false>(1, one), adj(one));
+  // known answers of test/prob/poisson/poisson_test.hpp:11-30 and test/prob/bernoulli/bernoulli_test.hpp:11-35
+  std::vector<int> n17{17}, n1{1};
+  std::vector<double> l13{13.0}, t25{0.25};
+  EXPECT_NEAR(-2.900934373290765311282, poisson_lpmf(n17, l13), 1e-13);
+  EXPECT_NEAR(std::log(0.25), bernoulli_lpmf(n1, t25), 1e-14);
+  stan::math::recover_memory();
+}
+
+TEST(CudaIntDensity, poisson_and_bernoulli_same_exceptions_and_log_zero_as_the_reference) {
+  using namespace stan::math;  // NOLINT
+  const int n = 2000;
+  std::vector<int> y(n, 1), y_two = y, y_neg = y;
+  y_two[1500] = 2;
+  y_neg[3] = -1;
+  vector_v lambda = to_v(VectorXd::LinSpaced(n, 0.5, 3.0)), theta = to_v(VectorXd::LinSpaced(n, 0.05, 0.95));
+  vector_v lam_nan = to_v(VectorXd::LinSpaced(n, 0.5, 3.0)), lam_neg = to_v(VectorXd::LinSpaced(n, 0.5, 3.0));
+  lam_nan[1999] = NAN;
+  lam_neg[17] = -1e-5;
+  vector_v th_hi = to_v(VectorXd::LinSpaced(n, 0.05, 0.95)), th_lo = to_v(VectorXd::LinSpaced(n, 0.05, 0.95)),
+           th_inf = to_v(VectorXd::LinSpaced(n, 0.05, 0.95));
+  th_hi[9] = 1.001;
+  th_lo[9] = -0.001;
+  th_inf[9] = INFINITY;
+  EXPECT_THROW(poisson_lpmf(y_neg, lambda), std::domain_error);
+  EXPECT_THROW(poisson_lpmf(y, lam_nan), std::domain_error);
+  EXPECT_THROW(poisson_lpmf(y, lam_neg), std::domain_error);
+  EXPECT_THROW(bernoulli_lpmf(y_two, theta), std::domain_error);
+  EXPECT_THROW(bernoulli_lpmf(y_neg, theta), std::domain_error);
+  EXPECT_THROW(bernoulli_lpmf(y, th_hi), std::domain_error);
+  EXPECT_THROW(bernoulli_lpmf(y, th_lo), std::domain_error);
+  EXPECT_THROW(bernoulli_lpmf(y, th_inf), std::domain_error);
+  vector_v shorter = to_v(VectorXd::LinSpaced(n - 1, 0.1, 0.9));
+  EXPECT_THROW(poisson_lpmf(y, shorter), std::invalid_argument);
+  EXPECT_THROW(bernoulli_lpmf(y, shorter), std::invalid_argument);
+  std::string m_gpu, m_cpu;
+  try {
+    poisson_lpmf(y, lam_neg);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    poisson_lpmf_reference_cpu<false>(y, lam_neg);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  m_gpu.clear();
+  m_cpu.clear();
+  try {
+    bernoulli_lpmf(y, th_hi);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    bernoulli_lpmf_reference_cpu<false>(y, th_hi);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  // LOG_ZERO early returns of poisson_lpmf.hpp:45-54
+  vector_v l_inf = to_v(VectorXd::Constant(n, 1.1)), l_zero = to_v(VectorXd::Constant(n, 1.1));
+  l_inf[7] = INFINITY;
+  l_zero[7] = 0.0;
+  EXPECT_EQ(LOG_ZERO, poisson_lpmf(y, l_inf).val());
+  EXPECT_EQ(LOG_ZERO, poisson_lpmf(y, l_zero).val());
+  std::vector<int> y0 = y;
+  y0[7] = 0;  // a zero rate next to a zero count contributes nothing (:59)
+  var lp = poisson_lpmf(y0, l_zero);
+  var lp_ref = poisson_lpmf_reference_cpu<false>(y0, l_zero);
+  EXPECT_TRUE(std::isfinite(lp.val()));
+  expect_rel(lp.val(), lp_ref.val(), std::fabs(lp_ref.val()), "zero rate with zero count");
+  std::vector<int> none;
+  vector_v empty(0);
+  EXPECT_EQ(0.0, poisson_lpmf(none, empty).val());
+  EXPECT_EQ(0.0, bernoulli_lpmf(none, empty).val());
+  stan::math::recover_memory();
+}
+
 // --- map_rect: shards dispatched to devices ------------------------------------------------------
 struct glm_shard {
   template <typename T1, typename T2>

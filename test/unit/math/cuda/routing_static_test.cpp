@@ -65,7 +65,7 @@ static_assert(cu::student_t_lpdf_eligible<vector_v, vector_v, vector_v, vector_v
 static_assert(cu::student_t_lpdf_eligible<double, double, vector_d, double>::value, "all data");
 static_assert(!cu::student_t_lpdf_eligible<double, var, var, var>::value, "scalar call stays on the reference loops");
 static_assert(!cu::student_t_lpdf_eligible<vector_d, vector_fd, double, double>::value, "fvar");
-// vectorised bernoulli_logit_lpmf / poisson_log_lpmf: container operand of double / var
+// vectorised bernoulli_logit_lpmf / poisson_log_lpmf / poisson_lpmf / bernoulli_lpmf: container operand of double / var
 static_assert(cu::int_density_eligible<ints, vector_v>::value, "d1 signature");
 static_assert(cu::int_density_eligible<int, std::vector<var>>::value, "scalar n");
 static_assert(cu::int_density_eligible<vector_i, vector_d>::value, "Eigen int n, double operand");
@@ -81,6 +81,10 @@ static_assert(std::is_same<decltype(stan::math::normal_id_glm_lpdf(vector_d(), m
 static_assert(std::is_same<decltype(stan::math::normal_lpdf(vector_d(), vector_v(), 1.0)), var>::value, "");
 static_assert(std::is_same<decltype(stan::math::bernoulli_logit_lpmf(ints(), vector_d())), double>::value, "");
 static_assert(std::is_same<decltype(stan::math::poisson_log_lpmf(ints(), vector_fd())), fvar<double>>::value, "");
+static_assert(std::is_same<decltype(stan::math::poisson_lpmf(ints(), vector_v())), var>::value, "");
+static_assert(std::is_same<decltype(stan::math::poisson_lpmf<true>(ints(), vector_d())), double>::value, "");
+static_assert(std::is_same<decltype(stan::math::bernoulli_lpmf(ints(), vector_fd())), fvar<double>>::value, "");
+static_assert(std::is_same<decltype(stan::math::bernoulli_lpmf(1, std::vector<var>())), var>::value, "");
 
 int main() {
   // anything not eligible runs the reference body in this very binary: no device is touched
@@ -89,8 +93,9 @@ int main() {
   vector_fd th(3);
   th << fvar<double>(0.1, 1.0), fvar<double>(0.2, 1.0), fvar<double>(-0.3, 1.0);
   const fvar<double> lf = stan::math::bernoulli_logit_lpmf(y, th);  // fvar -> reference loop
-  std::printf("routing_static_test PASSED (%.6f %.6f %.6f)\n", lp, lf.val_, lf.d_);
-  return (lp < 0 && lf.val_ < 0) ? 0 : 1;
+  const double lq = stan::math::bernoulli_lpmf(y, 0.3) + stan::math::poisson_lpmf(y, 1.5);  // scalar operands -> reference loops
+  std::printf("routing_static_test PASSED (%.6f %.6f %.6f %.6f)\n", lp, lf.val_, lf.d_, lq);
+  return (lp < 0 && lf.val_ < 0 && lq < 0) ? 0 : 1;
 }
 #else
 int main() { return 1; }

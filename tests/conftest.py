@@ -20,6 +20,13 @@ def golden_st():
 
 
 @pytest.fixture(scope="session")
+def golden_d2():
+    """poisson_lpmf / bernoulli_lpmf vectors from the compiled reference (tests/golden/make_density2_golden.py)."""
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "density2_golden.npz"), allow_pickle=False)
+
+
+@pytest.fixture(scope="session")
 def golden():
     import numpy as np
     path = os.path.join(ROOT, "tests", "golden", "glm_golden.npz")

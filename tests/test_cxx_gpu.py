@@ -26,7 +26,8 @@ BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_po
             "cuda_tri_solve_test", "ref_mdivide_left_tri_test", "ref_mdivide_right_tri_test", "ref_mix_mdivide_left_tri_test",
             "cuda_gp_exp_quad_cov_test", "ref_gp_exp_quad_cov_test", "ref_rev_gp_exp_quad_cov_test",
             "ref_mix_mdivide_left_tri_low_test",
-            "ref_multi_normal_cholesky_test", "ref_rev_multi_normal_cholesky_test"]
+            "ref_multi_normal_cholesky_test", "ref_rev_multi_normal_cholesky_test",
+            "cuda_int_density2_distr_test", "ref_poisson_test", "ref_bernoulli_test", "ref_bernoulli_log_test"]
 
 
 @pytest.mark.gpu

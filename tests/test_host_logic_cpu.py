@@ -10,9 +10,10 @@ from oracle import loader as L
 needs_ref = pytest.mark.skipif(not L.have_ref(), reason="oracle/_ref/libstanref.so not built")
 
 
-@pytest.mark.parametrize("f,kw", [(glm.bernoulli_logit_lpmf, "theta_var"), (glm.poisson_log_lpmf, "alpha_var")])
+@pytest.mark.parametrize("f,kw", [(glm.bernoulli_logit_lpmf, "theta_var"), (glm.poisson_log_lpmf, "alpha_var"),
+                                  (glm.poisson_lpmf, "lambda_var"), (glm.bernoulli_lpmf, "theta_var")])
 def test_density_paths_that_need_no_device(f, kw):
-    th = np.linspace(-1, 1, 10)
+    th = np.linspace(-1, 1, 10) if f in (glm.bernoulli_logit_lpmf, glm.poisson_log_lpmf) else np.linspace(0.1, 0.9, 10)
     ones = np.ones(10, dtype=np.int32)
     assert f([], [])[0] == 0.0                                           # size_zero(n, theta)
     assert f(ones, [])[0] == 0.0
@@ -30,12 +31,17 @@ def test_density_paths_that_need_no_device(f, kw):
         f(ones[:7], nan)
     with pytest.raises(glm.DomainError):                                # checks run even when nothing is computed
         f(bad, th[:7], propto=True, **{kw: False})
+    if f in (glm.poisson_lpmf, glm.bernoulli_lpmf):                     # the operand's own range check (rate >= 0, probability in [0, 1])
+        neg = th.copy()
+        neg[4] = -0.5
+        with pytest.raises(glm.DomainError):
+            f(ones, neg, propto=True, **{kw: False})
 
 
 @needs_ref
-@pytest.mark.parametrize("density", ["bernoulli_logit", "poisson_log"])
+@pytest.mark.parametrize("density", ["bernoulli_logit", "poisson_log", "poisson", "bernoulli"])
 def test_reference_reacts_the_same_way(density):
-    th = np.linspace(-1, 1, 10)
+    th = np.linspace(-1, 1, 10) if density.endswith(("logit", "log")) else np.linspace(0.1, 0.9, 10)
     ones = np.ones(10, dtype=np.int32)
     with pytest.raises(L.RefError) as e:
         L.ref_density(density, ones[:7], th)

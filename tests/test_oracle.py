@@ -124,6 +124,61 @@ def test_oracle_densities_match_golden_and_known_answers(golden):
     assert known == 10
 
 
+def test_oracle_poisson_and_bernoulli_match_golden_and_known_answers(golden_d2):
+    """poisson_lpmf / bernoulli_lpmf: outputs of the compiled reference, and the literal expected values of the
+    reference's own tests (test/prob/poisson/poisson_test.hpp:11-30, test/prob/bernoulli/bernoulli_test.hpp:11-35)."""
+    assert len(golden_d2["dens_cases"]) >= 18
+    known = 0
+    for name in golden_d2["dens_cases"]:
+        c = dens_case(golden_d2, str(name))
+        r = L.oracle_density(c["density"], c["y"], c["theta"], propto=c["propto"])
+        assert r["rc"] == 0, name
+        check_dens_result(r, c, "oracle vs golden dens " + str(name), rtol=1e-12)
+        if "known_answer" in c:
+            known += 1
+            assert abs(r["lp"] - c["known_answer"]) <= 1e-13 * max(1.0, abs(c["known_answer"])), name
+    assert known == 7
+
+
+def test_oracle_poisson_and_bernoulli_codes():
+    """What the product must report where the reference throws (poisson_lpmf.hpp:31-33, bernoulli_lpmf.hpp:41-43; the
+    invalid values of test/prob/poisson/poisson_test.hpp:32-43, test/prob/bernoulli/bernoulli_test.hpp:37-51) or
+    returns LOG_ZERO (poisson_lpmf.hpp:45-54)."""
+    for bad_n, bad_t in (([-1], [1.0]), ([1], [-1e-5]), ([1], [-1.0]), ([1, 2], [1.0, np.nan])):
+        assert L.oracle_density("poisson", bad_n, bad_t)["rc"] == _abi.BAD_OPERAND
+    for bad_n, bad_t in (([-1], [0.5]), ([2], [0.5]), ([1], [-0.001]), ([1], [1.001]), ([1, 0], [0.5, np.nan]), ([1], [np.inf])):
+        assert L.oracle_density("bernoulli", bad_n, bad_t)["rc"] == _abi.BAD_OPERAND
+    r = L.oracle_density("poisson", [1, 2], [np.inf, 0.1])
+    assert r["rc"] == _abi.LOG_ZERO and r["lp"] == -np.inf
+    assert L.oracle_density("poisson", [1, 2], [0.0, 0.1])["rc"] == _abi.LOG_ZERO
+    assert L.oracle_density("poisson", [0, 2], [0.0, 0.1])["rc"] == 0
+    assert L.oracle_density("poisson", [], [])["lp"] == 0.0 and L.oracle_density("bernoulli", [], [])["lp"] == 0.0
+    # the corners of the support are legal: log(0) = -inf where the outcome contradicts a certain probability
+    assert L.oracle_density("bernoulli", [1, 0], [1.0, 0.0])["lp"] == 0.0
+    assert L.oracle_density("bernoulli", [0], [1.0])["lp"] == -np.inf
+
+
+@needs_ref
+@pytest.mark.parametrize("density", ["poisson", "bernoulli"])
+def test_oracle_poisson_and_bernoulli_vs_compiled_reference(density):
+    rng = np.random.default_rng(4)
+    n = 5000
+    theta = rng.gamma(2.0, 1.5, n) if density == "poisson" else rng.uniform(0.02, 0.98, n)
+    y = rng.poisson(2.0, n).astype(np.int32) if density == "poisson" else (rng.random(n) < 0.4).astype(np.int32)
+    for propto in (False, True):
+        for yy, th in ((y, theta), (y, theta[:1]), (y[:1], theta)):
+            ref = L.ref_density(density, yy, th, propto=propto)
+            got = L.oracle_density(density, yy, th, propto=propto)
+            assert got["rc"] == 0
+            assert_close(got["lp"], ref["lp"], "%s lp" % density, 1e-12)
+            assert_close(got["dtheta"], ref["dtheta"], "%s dtheta" % density, 1e-12)
+    if density == "poisson":   # a zero rate next to a zero count: the term is skipped (:59), the partial is 0/0 - 1
+        ref = L.ref_density("poisson", [0, 2, 0], [0.0, 0.1, 0.4])
+        got = L.oracle_density("poisson", [0, 2, 0], [0.0, 0.1, 0.4])
+        assert got["lp"] == ref["lp"] and np.array_equal(got["dtheta"], ref["dtheta"], equal_nan=True)
+        assert np.isnan(ref["dtheta"][0])
+
+
 def test_oracle_density_codes():
     """What the product must report where the reference throws or returns LOG_ZERO."""
     assert L.oracle_density("bernoulli_logit", [2], [0.1])["rc"] == _abi.BAD_OPERAND
