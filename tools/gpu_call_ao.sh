@@ -1,5 +1,5 @@
 #!/bin/bash
-# final validation of the tree + 8 copy threads A/B + ncu --set full of the default DGEMM kernel
+# final validation of the tree
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -5 > gpurun_out/ao_pytest.log
 cat gpurun_out/ao_pytest.log
