@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|d3|d4|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|d3|d4|l1|l2|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -360,6 +360,27 @@ double normal_once(const VectorXd& y, const VectorXd& mu_val, double sigma_val, 
   return t1 - t0;
 }
 
+// cauchy_lpdf (DENSITY 1) / lognormal_lpdf (2) as a model states them -- data y, var vector mu, var sigma
+template <bool GPU, int DENSITY>
+double locscale_once(const VectorXd& y, const VectorXd& mu_val, double sigma_val, Result* out) {
+  using namespace stan::math;  // NOLINT
+  start_nested();
+  vector_v mu(mu_val.size());
+  for (int64_t i = 0; i < mu_val.size(); ++i) mu[i] = mu_val[i];
+  var sigma = sigma_val;
+  const double t0 = now();
+  var lp = DENSITY == 1 ? (GPU ? cauchy_lpdf(y, mu, sigma) : cauchy_lpdf_reference_cpu<false>(y, mu, sigma))
+                        : (GPU ? lognormal_lpdf(y, mu, sigma) : lognormal_lpdf_reference_cpu<false>(y, mu, sigma));
+  grad(lp.vi_);
+  out->lp = lp.val();
+  out->grad.resize(mu.size() + 1);
+  for (int64_t i = 0; i < mu.size(); ++i) out->grad[i] = mu[i].adj();
+  out->grad[mu.size()] = sigma.adj();
+  const double t1 = now();
+  recover_memory_nested();
+  return t1 - t0;
+}
+
 // student_t_lpdf as a model states it -- data y, var nu, var vector mu, var sigma; one evaluation =
 // forward + grad() + reading the N + 2 adjoints
 template <bool GPU>
@@ -559,6 +580,32 @@ int run(int argc, char** argv) {
     print_timing("gpu", tg);
     if (!no_cpu) {
       Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, [&] { return normal_once<false>(y, mu, 1.3, &c); });
+      std::printf(", ");
+      print_timing("cpu_reference_1_thread", tc);
+      std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));
+    }
+    std::printf(", \"algorithmic_device_bytes\": %lld}\n", (long long)(3 * n * 8));
+    return 0;
+  }
+
+  if (config == "l1" || config == "l2") {  // cauchy_lpdf, lognormal_lpdf
+    const bool cauchy = config == "l1";
+    const int64_t n = n_override ? n_override : 1000000;
+    VectorXd y(n), mu(n);
+    Rng r(cauchy ? 1041 : 1042);
+    for (int64_t i = 0; i < n; ++i) {
+      y[i] = cauchy ? 2.0 * r.normal() : std::exp(1.2 * r.normal());
+      mu[i] = 0.1 * r.normal();
+    }
+    Result g, c;
+    auto gpu = [&] { return cauchy ? locscale_once<true, 1>(y, mu, 1.3, &g) : locscale_once<true, 2>(y, mu, 1.3, &g); };
+    auto cpu = [&] { return cauchy ? locscale_once<false, 1>(y, mu, 1.3, &c) : locscale_once<false, 2>(y, mu, 1.3, &c); };
+    gpu();
+    Timing tg = time_reps(3, reps, 30, gpu);
+    std::printf("\"what\": \"%s N=%lld, y data, mu var vector, sigma var\", ", cauchy ? "cauchy_lpdf" : "lognormal_lpdf", (long long)n);
+    print_timing("gpu", tg);
+    if (!no_cpu) {
+      Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, cpu);
       std::printf(", ");
       print_timing("cpu_reference_1_thread", tc);
       std::printf(", \"parity_rel_err\": %.3e", rel_err(g, c));

@@ -182,6 +182,15 @@ typedef struct stan_cuda_normal_args {
   double* dy;          /* [y_len] */
 } stan_cuda_normal_args;
 
+/* Location-scale densities that share stan_cuda_normal_args: the density id selects the
+ * per-element term of stan_cuda_locscale_lpdf_eval; stan_cuda_normal_lpdf_eval is id 0. */
+#define STAN_CUDA_LOCSCALE_NORMAL 0    /* normal_lpdf(y | mu, sigma)     prim/scal/prob/normal_lpdf.hpp:38-113 */
+#define STAN_CUDA_LOCSCALE_CAUCHY 1    /* cauchy_lpdf(y | mu, sigma)     prim/scal/prob/cauchy_lpdf.hpp:35-113 */
+#define STAN_CUDA_LOCSCALE_LOGNORMAL 2 /* lognormal_lpdf(y | mu, sigma)  prim/scal/prob/lognormal_lpdf.hpp:19-133 */
+/* lognormal only: the -sum log(y) term, which the reference ties to include_summand<propto, T_y>
+ * (lognormal_lpdf.hpp:113-115) */
+#define STAN_CUDA_LP_Y 0x1000u
+
 /* Vectorised elementwise densities with an integer outcome and one real operand: value + partials of the
  * operand in one pass (the pattern of stan_cuda_normal_lpdf_eval for the lpmf's whose
  * per-element terms are the epilogues of the GLM kernels). */
@@ -311,6 +320,12 @@ STAN_CUDA_API int stan_cuda_glm_eval(const stan_cuda_glm_args* a);
  * worst of them (or a negative error, after which no output is valid). */
 STAN_CUDA_API int stan_cuda_glm_eval_batch(const stan_cuda_glm_args* items, int count, int call_id, int* item_rc);
 STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
+/* The same call for the other location-scale densities (density: STAN_CUDA_LOCSCALE_*).  Flags as for normal_lpdf:
+ * LP_CONST = the constant (N * NEG_LOG_SQRT_TWO_PI | N * NEG_LOG_PI), LP_SCALE = -sum log(sigma), LP_MAIN = the
+ * term every operand enters, LP_Y (lognormal) = -sum log(y).  Returns STAN_CUDA_BAD_OPERAND where the reference's
+ * eager checks throw (cauchy_lpdf.hpp:47-49: y NaN, mu not finite, sigma not positive and finite; lognormal_lpdf.hpp:24-27:
+ * also y negative) and STAN_CUDA_LOG_ZERO for lognormal_lpdf with an outcome equal to zero (:41-45). */
+STAN_CUDA_API int stan_cuda_locscale_lpdf_eval(int32_t density, const stan_cuda_normal_args* a);
 /* Returns STAN_CUDA_BAD_OPERAND when an outcome is outside the density's support (bernoulli_logit: not in
  * {0, 1}, bernoulli_logit_lpmf.hpp:42; poisson_log: negative, poisson_log_lpmf.hpp:38) or the operand is NaN
  * (:43 / :39; poisson: NaN or negative rate, poisson_lpmf.hpp:32-33; bernoulli: probability not finite or outside

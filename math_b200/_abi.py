@@ -116,6 +116,9 @@ class MultiplyArgs(C.Structure):
     ]
 
 
+LOCSCALE_NORMAL, LOCSCALE_CAUCHY, LOCSCALE_LOGNORMAL = 0, 1, 2
+LOCSCALES = {"normal": LOCSCALE_NORMAL, "cauchy": LOCSCALE_CAUCHY, "lognormal": LOCSCALE_LOGNORMAL}
+LP_Y = 0x1000
 DENSITY_BERNOULLI_LOGIT, DENSITY_POISSON_LOG, DENSITY_POISSON, DENSITY_BERNOULLI = 1, 2, 3, 4
 DENSITIES = {"bernoulli_logit": DENSITY_BERNOULLI_LOGIT, "poisson_log": DENSITY_POISSON_LOG, "poisson": DENSITY_POISSON,
              "bernoulli": DENSITY_BERNOULLI}
@@ -165,6 +168,7 @@ PROTOTYPES = {
     "stan_cuda_glm_eval": (C.c_int, [C.POINTER(GlmArgs)]),
     "stan_cuda_glm_eval_batch": (C.c_int, [C.POINTER(GlmArgs), C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "stan_cuda_density_eval": (C.c_int, [C.POINTER(DensityArgs)]),
+    "stan_cuda_locscale_lpdf_eval": (C.c_int, [C.c_int32, C.POINTER(NormalArgs)]),
     "stan_cuda_normal_lpdf_eval": (C.c_int, [C.POINTER(NormalArgs)]),
     "stan_cuda_student_t_lpdf_eval": (C.c_int, [C.POINTER(StudentTArgs)]),
     "stan_cuda_matrix_create": (C.c_int, [C.c_int64, C.c_int64, C.POINTER(C.c_void_p)]),

@@ -869,9 +869,15 @@ static int vec_to_host(double* host, const double* dev, int64_t n, cudaStream_t 
   return STAN_CUDA_OK;
 }
 
-int normal_lpdf_eval(const stan_cuda_normal_args* a) {
-  NvtxRange range("stan_cuda_normal_lpdf_eval");
+int locscale_lpdf_eval(int family, const stan_cuda_normal_args* a);
+int normal_lpdf_eval(const stan_cuda_normal_args* a) { return locscale_lpdf_eval(STAN_CUDA_LOCSCALE_NORMAL, a); }
+
+// normal_lpdf / cauchy_lpdf / lognormal_lpdf: three real operands, each a scalar or a vector of n
+int locscale_lpdf_eval(int family, const stan_cuda_normal_args* a) {
+  NvtxRange range("stan_cuda_locscale_lpdf_eval");
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: null args");
+  if (family < STAN_CUDA_LOCSCALE_NORMAL || family > STAN_CUDA_LOCSCALE_LOGNORMAL)
+    return fail(STAN_CUDA_ERR_ARG, "stan_cuda_locscale_lpdf_eval: unknown density");
   if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: negative n");
   if (a->n == 0) {  // size_zero(y, mu, sigma) -> 0 (normal_lpdf.hpp:45-47)
     if (a->lp) *a->lp = 0.0;
@@ -907,6 +913,7 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   double* p = td->d_buf;
   NormalIO io{};
   io.flags = a->flags;
+  io.family = family;
   io.n = n;
   io.result = p; p += 8;
   io.y_vec = yv; io.mu_vec = mv; io.sigma_vec = sv;
@@ -931,7 +938,7 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   if (need_sigma && sv) { io.dsigma_row = p; p += nal; }
   if (need_y && yv) { io.dy_row = p; p += nal; }
   SC_TRY(launch_normal_lpdf(io, &td->ws, dev, td->stream));
-  SC_CUDA(cudaMemcpyAsync(td->h_pinned, io.result, 5 * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
+  SC_CUDA(cudaMemcpyAsync(td->h_pinned, io.result, 6 * sizeof(double), cudaMemcpyDeviceToHost, td->stream));
   if (io.dmu_row) SC_TRY(vec_to_host(a->dmu, io.dmu_row, n, td->stream));
   if (io.dsigma_row) SC_TRY(vec_to_host(a->dsigma, io.dsigma_row, n, td->stream));
   if (io.dy_row) SC_TRY(vec_to_host(a->dy, io.dy_row, n, td->stream));
@@ -939,10 +946,15 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) {
   const double* res = td->h_pinned;
   if (a->lp) *a->lp = res[0];
   if (need_mu && !mv) a->dmu[0] = res[1];
-  if (need_y && !yv) a->dy[0] = -res[1];
+  if (need_y && !yv) a->dy[0] = family == STAN_CUDA_LOCSCALE_LOGNORMAL ? res[5] : -res[1];
   if (need_sigma && !sv) a->dsigma[0] = res[2];
   counters().evals.fetch_add(1, std::memory_order_relaxed);
-  if (res[4] != 0.0) return STAN_CUDA_BAD_OPERAND;
+  const unsigned bits = unsigned(res[4]);
+  if (bits & 7u) return STAN_CUDA_BAD_OPERAND;
+  if (bits & 8u) {  // lognormal_lpdf with an outcome equal to zero: LOG_ZERO, no partials (lognormal_lpdf.hpp:41-45)
+    if (a->lp) *a->lp = -INFINITY;
+    return STAN_CUDA_LOG_ZERO;
+  }
   return isfinite(res[3]) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
@@ -1200,6 +1212,7 @@ int stan_cuda_glm_eval_batch(const stan_cuda_glm_args* items, int count, int cal
 int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) { return normal_lpdf_eval(a); }
 int stan_cuda_student_t_lpdf_eval(const stan_cuda_student_t_args* a) { return student_t_lpdf_eval(a); }
 int stan_cuda_density_eval(const stan_cuda_density_args* a) { return density_eval(a); }
+int stan_cuda_locscale_lpdf_eval(int32_t density, const stan_cuda_normal_args* a) { return locscale_lpdf_eval(density, a); }
 void* stan_cuda_host_staging(size_t bytes) { return host_staging(bytes); }
 
 int stan_cuda_cache_invalidate(const void* host_ptr) {

@@ -194,13 +194,14 @@ int upload_glm_data(stan_cuda_data* d, const double* x, int64_t ldx, int x_row_m
 // normal_lpdf kernel (normal_kernel.cu)
 struct NormalIO {
   uint32_t flags;
+  int family;                 // STAN_CUDA_LOCSCALE_*
   int64_t n;
   const double* y; int y_vec;
   const double* mu; int mu_vec;
   const double* sigma; int sigma_vec;
   double y0, mu0, sigma0;     // scalar operands by value
   double* dmu_row; double* dsigma_row; double* dy_row;  // per-row outputs (vector operands) or null
-  double* result;             // [4]: lp, sum scaled_diff, sum dsigma, witness
+  double* result;             // [6]: lp, sum dmu, sum dsigma, witness, status bits, sum dy
 };
 int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream_t stream);
 

@@ -1,5 +1,5 @@
-// normal_lpdf.cu -- vectorised normal_lpdf value + partials in one pass
-// (stan/math/prim/scal/prob/normal_lpdf.hpp:78-110).  Elementwise map + fixed-order reduction;
+// normal_lpdf.cu -- vectorised normal_lpdf (and, same operands, cauchy_lpdf / lognormal_lpdf) value + partials in one
+// pass (stan/math/prim/scal/prob/normal_lpdf.hpp:78-110).  Elementwise map + fixed-order reduction;
 // each operand is either a device vector or a scalar passed by value.  Per-row partials are
 // written only for vector operands; scalar operands get the sum (the reference accumulates them
 // through broadcast_array, prim/scal/meta/broadcast_array.hpp:9-33).
@@ -11,69 +11,106 @@ namespace stancuda {
 
 struct NormalKernelParams {
   NormalIO io;
-  double* scratch;       // [grid][4]
+  double* scratch;       // [grid][8]
   unsigned int* ticket;
 };
 
-template <int THREADS>
+// FAMILY: STAN_CUDA_LOCSCALE_NORMAL | CAUCHY | LOGNORMAL -- the same three operands, the same operand handling, a
+// different per-element term:
+//   cauchy_lpdf     stan/math/prim/scal/prob/cauchy_lpdf.hpp:60-108
+//   lognormal_lpdf  stan/math/prim/scal/prob/lognormal_lpdf.hpp:41-131
+template <int FAMILY, int THREADS>
 __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernelParams p) {
   const NormalIO& io = p.io;
   const double NEG_LOG_SQRT_TWO_PI = -0.91893853320467274178032973640561763986;
+  const double NEG_LOG_PI = -1.14472988584940017414342735135;
   const bool lp_const = io.flags & STAN_CUDA_LP_CONST, lp_scale = io.flags & STAN_CUDA_LP_SCALE,
-             lp_main = io.flags & STAN_CUDA_LP_MAIN;
-  double a_lp = 0.0, a_sd = 0.0, a_ds = 0.0;  // lp, sum scaled_diff, sum dsigma
+             lp_main = io.flags & STAN_CUDA_LP_MAIN, lp_y = io.flags & STAN_CUDA_LP_Y;
+  double a_lp = 0.0, a_sd = 0.0, a_ds = 0.0, a_dy = 0.0;  // lp, sum dmu, sum dsigma, sum dy
   // domain of the operands, checked here instead of in three O(N) host loops
-  // (check_not_nan(y), check_finite(mu), check_positive(sigma): normal_lpdf.hpp:51-53)
-  unsigned bad = 0;  // bit 0: y is NaN, bit 1: mu not finite, bit 2: sigma not > 0
+  // (check_not_nan(y), check_finite(mu), check_positive(sigma): normal_lpdf.hpp:51-53; cauchy / lognormal:
+  // check_positive_finite(sigma), lognormal also check_nonnegative(y))
+  unsigned bad = 0;  // bit 0: y is NaN (lognormal: or negative), bit 1: mu not finite, bit 2: sigma outside its domain,
+                     // bit 3: lognormal with an outcome equal to zero (LOG_ZERO, lognormal_lpdf.hpp:41-45)
   const double inv_sigma0 = 1.0 / io.sigma0, log_sigma0 = log(io.sigma0);
   for (int64_t i = blockIdx.x * int64_t(THREADS) + threadIdx.x; i < io.n; i += int64_t(gridDim.x) * THREADS) {
     const double y = io.y_vec ? io.y[i] : io.y0;
     const double mu = io.mu_vec ? io.mu[i] : io.mu0;
-    double inv_sigma = inv_sigma0, log_sigma = log_sigma0;
+    double sg = io.sigma0, inv_sigma = inv_sigma0, log_sigma = log_sigma0;
     if (io.sigma_vec) {
-      const double sg = io.sigma[i];
+      sg = io.sigma[i];
       inv_sigma = 1.0 / sg;
       if (lp_scale) log_sigma = log(sg);
     }
     bad |= (isnan(y) ? 1u : 0u) | (isfinite(mu) ? 0u : 2u);
-    if (io.sigma_vec) bad |= (io.sigma[i] > 0.0) ? 0u : 4u;
-    const double z = (y - mu) * inv_sigma;           // :82-83
-    const double z2 = z * z;
-    double lp = 0.0;
-    if (lp_const) lp += NEG_LOG_SQRT_TWO_PI;         // :89-91
-    if (lp_scale) lp -= log_sigma;                   // :92-94
-    if (lp_main) lp += -0.5 * z2;                    // :95-97
+    if (io.sigma_vec) bad |= (sg > 0.0 && (FAMILY == STAN_CUDA_LOCSCALE_NORMAL || isfinite(sg))) ? 0u : 4u;
+    double lp = 0.0, d_mu, d_sigma, d_y;
+    if (FAMILY == STAN_CUDA_LOCSCALE_NORMAL) {
+      const double z = (y - mu) * inv_sigma;           // :82-83
+      const double z2 = z * z;
+      if (lp_const) lp += NEG_LOG_SQRT_TWO_PI;         // :89-91
+      if (lp_scale) lp -= log_sigma;                   // :92-94
+      if (lp_main) lp += -0.5 * z2;                    // :95-97
+      d_mu = inv_sigma * z;                            // :99, :104
+      d_sigma = -inv_sigma + inv_sigma * z2;           // :108
+      d_y = -d_mu;                                     // :101
+    } else if (FAMILY == STAN_CUDA_LOCSCALE_CAUCHY) {
+      const double sigma_squared = sg * sg;            // :69
+      const double y_minus_mu = y - mu;                // :81-85
+      const double y_minus_mu_squared = y_minus_mu * y_minus_mu;
+      const double z = y_minus_mu * inv_sigma;
+      if (lp_const) lp += NEG_LOG_PI;                  // :87-89
+      if (lp_scale) lp -= log_sigma;                   // :90-92
+      if (lp_main) lp -= log1p(z * z);                 // :93-95
+      d_mu = 2.0 * y_minus_mu / (sigma_squared + y_minus_mu_squared);                                   // :101-104
+      d_y = -d_mu;                                                                                      // :97-100
+      d_sigma = (y_minus_mu_squared - sigma_squared) * inv_sigma / (sigma_squared + y_minus_mu_squared);  // :105-109
+    } else {
+      bad |= (y < 0.0) ? 1u : 0u;                      // :25 check_nonnegative(y)
+      bad |= (y == 0.0) ? 8u : 0u;                     // :41-45
+      const double log_y = log(y), inv_y = 1.0 / y;    // :78-90
+      const double inv_sigma_sq = inv_sigma * inv_sigma;
+      const double logy_m_mu = log_y - mu;             // :99-102
+      const double logy_m_mu_div_sigma = logy_m_mu * inv_sigma_sq;  // :105-108
+      if (lp_const) lp += NEG_LOG_SQRT_TWO_PI;         // :92-94 (N times the constant)
+      if (lp_scale) lp -= log_sigma;                   // :110-112
+      if (lp_y) lp -= log_y;                           // :113-115
+      if (lp_main) lp -= 0.5 * (logy_m_mu * logy_m_mu) * inv_sigma_sq;  // :116-118
+      d_y = -(1.0 + logy_m_mu_div_sigma) * inv_y;      // :120-122
+      d_mu = logy_m_mu_div_sigma;                      // :123-125
+      d_sigma = (logy_m_mu_div_sigma * logy_m_mu - 1.0) * inv_sigma;  // :126-129
+    }
     a_lp += lp;
-    const double scaled_diff = inv_sigma * z;        // :99
-    const double ds = -inv_sigma + inv_sigma * z2;   // :108
-    a_sd += scaled_diff;
-    a_ds += ds;
-    if (io.dmu_row) io.dmu_row[i] = scaled_diff;     // :104
-    if (io.dy_row) io.dy_row[i] = -scaled_diff;      // :101
-    if (io.dsigma_row) io.dsigma_row[i] = ds;
+    a_sd += d_mu;
+    a_ds += d_sigma;
+    a_dy += d_y;
+    if (io.dmu_row) io.dmu_row[i] = d_mu;
+    if (io.dy_row) io.dy_row[i] = d_y;
+    if (io.dsigma_row) io.dsigma_row[i] = d_sigma;
   }
   // block reduction in fixed order
-  __shared__ double sh[3][THREADS / 32];
+  __shared__ double sh[4][THREADS / 32];
   __shared__ int s_is_last;
   __shared__ unsigned s_bad;
-  if (threadIdx.x == 0) s_bad = (io.sigma_vec || io.sigma0 > 0.0) ? 0u : 4u;
+  if (threadIdx.x == 0)
+    s_bad = (io.sigma_vec || (io.sigma0 > 0.0 && (FAMILY == STAN_CUDA_LOCSCALE_NORMAL || isfinite(io.sigma0)))) ? 0u : 4u;
   __syncthreads();
   bad = __reduce_or_sync(0xffffffffu, bad);
   if ((threadIdx.x & 31) == 0 && bad) atomicOr(&s_bad, bad);
-  double v[3] = {a_lp, a_sd, a_ds};
+  double v[4] = {a_lp, a_sd, a_ds, a_dy};
 #pragma unroll
-  for (int q = 0; q < 3; ++q) {
+  for (int q = 0; q < 4; ++q) {
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], off);
     if ((threadIdx.x & 31) == 0) sh[q][threadIdx.x >> 5] = v[q];
   }
   __syncthreads();
-  if (threadIdx.x < 3) {
+  if (threadIdx.x < 4) {
     double s = 0.0;
     for (int w = 0; w < THREADS / 32; ++w) s += sh[threadIdx.x][w];
-    p.scratch[size_t(blockIdx.x) * 4 + threadIdx.x] = s;
+    p.scratch[size_t(blockIdx.x) * 8 + threadIdx.x] = s;
   }
-  if (threadIdx.x == 3) p.scratch[size_t(blockIdx.x) * 4 + 3] = double(s_bad);
+  if (threadIdx.x == 4) p.scratch[size_t(blockIdx.x) * 8 + 4] = double(s_bad);
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -84,21 +121,21 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
   if (!s_is_last) return;
   __threadfence();
   // warp q sums column q of the per-CTA partials: lane l takes CTAs l, l + 32, ... in order, then a shuffle tree
-  // (a fixed order: bit-reproducible from call to call); warp 3 ORs the bad-operand bits.  A single thread walking
+  // (a fixed order: bit-reproducible from call to call); warp 4 ORs the status bits.  A single thread walking
   // all 1184 partials cost more than the map itself at N = 1e6.
   const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  if (warp < 3u) {
+  if (warp < 4u) {
     double s = 0.0;
-    for (unsigned b = lane; b < gridDim.x; b += 32u) s += __ldcg(p.scratch + size_t(b) * 4 + warp);
+    for (unsigned b = lane; b < gridDim.x; b += 32u) s += __ldcg(p.scratch + size_t(b) * 8 + warp);
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
     if (lane == 0) {
-      io.result[warp] = s;
-      if (warp == 0) io.result[3] = s;  // finiteness witness = logp
+      io.result[warp == 3u ? 5 : warp] = s;  // [0] lp, [1] sum dmu, [2] sum dsigma, [5] sum dy
+      if (warp == 0) io.result[3] = s;       // finiteness witness = logp
     }
-  } else if (warp == 3u) {
+  } else if (warp == 4u) {
     unsigned all_bad = 0;
-    for (unsigned b = lane; b < gridDim.x; b += 32u) all_bad |= unsigned(__ldcg(p.scratch + size_t(b) * 4 + 3));
+    for (unsigned b = lane; b < gridDim.x; b += 32u) all_bad |= unsigned(__ldcg(p.scratch + size_t(b) * 8 + 4));
     all_bad = __reduce_or_sync(0xffffffffu, all_bad);
     if (lane == 0) io.result[4] = double(all_bad);
   }
@@ -112,9 +149,21 @@ int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream
   int64_t want = (io.n + THREADS * 4 - 1) / (THREADS * 4);
   int64_t cap = int64_t(sm_count(device)) * 8;
   const int grid = int(want < cap ? (want < 1 ? 1 : want) : cap);
-  SC_TRY(workspace_reserve(ws, device, size_t(grid) * 4));
+  SC_TRY(workspace_reserve(ws, device, size_t(grid) * 8));
   NormalKernelParams p{io, ws->scratch, ws->ticket};
-  normal_lpdf_kernel<THREADS><<<grid, THREADS, 0, stream>>>(p);
+  switch (io.family) {
+    case STAN_CUDA_LOCSCALE_NORMAL:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_NORMAL, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_LOCSCALE_CAUCHY:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_CAUCHY, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_LOCSCALE_LOGNORMAL:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_LOGNORMAL, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    default:
+      return fail(STAN_CUDA_ERR_ARG, "launch_normal_lpdf: unknown density");
+  }
   SC_CUDA(cudaGetLastError());
   counters().launches.fetch_add(1, std::memory_order_relaxed);
   return STAN_CUDA_OK;

@@ -434,6 +434,89 @@ def normal_lpdf(y, mu, sigma, propto=False, need_dy=False, y_is_data=True):
     return float(lp[0]), grads
 
 
+def locscale_eval(density, y, mu, sigma, flags, y_is_data=True):
+    """One stan_cuda_locscale_lpdf_eval call (density: "normal" | "cauchy" | "lognormal"); returns {"rc", "lp", "dy",
+    "dmu", "dsigma"} (partials for the NEED_* bits in flags, each the length of its operand)."""
+    d = _abi.LOCSCALES[density] if isinstance(density, str) else density
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    n = max(y.size, mu.size, sigma.size) if min(y.size, mu.size, sigma.size) > 0 else 0
+    a = _abi.NormalArgs()
+    lp = np.zeros(1)
+    dy, dmu, dsigma = np.zeros(max(y.size, 1)), np.zeros(max(mu.size, 1)), np.zeros(max(sigma.size, 1))
+    a.flags, a.y_is_data, a.n = flags, int(y_is_data), n
+    a.y, a.y_len, a.mu, a.mu_len = y.ctypes.data, y.size, mu.ctypes.data, mu.size
+    a.sigma, a.sigma_len = sigma.ctypes.data, sigma.size
+    a.lp, a.dmu, a.dsigma, a.dy = lp.ctypes.data, dmu.ctypes.data, dsigma.ctypes.data, dy.ctypes.data
+    rc = check(lib().stan_cuda_locscale_lpdf_eval(d, C.byref(a)))
+    res = {"rc": rc, "lp": float(lp[0])}
+    for key, bit, g, op in (("dy", _abi.NEED_DY, dy, y), ("dmu", _abi.NEED_DALPHA, dmu, mu), ("dsigma", _abi.NEED_DSIGMA, dsigma, sigma)):
+        if flags & bit:
+            res[key] = g[:op.size].copy()
+    return res
+
+
+def _locscale_lpdf(function, density, y, mu, sigma, propto, var_mask, y_is_data):
+    """Call sequence of cauchy_lpdf.hpp:42-58 / lognormal_lpdf.hpp:24-45: domain errors in the reference's order, then the
+    size error, nothing to compute -> 0 (lognormal: LOG_ZERO comes first), partials only for the variables."""
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    lognormal = density == "lognormal"
+    if min(y.size, mu.size, sigma.size) == 0 and not lognormal:
+        return 0.0, {}
+    if np.any(np.isnan(y)):
+        raise DomainError("%s: Random variable is nan" % function)
+    if lognormal and np.any(y < 0):
+        raise DomainError("%s: Random variable must be >= 0" % function)
+    if not np.all(np.isfinite(mu)):
+        raise DomainError("%s: Location parameter must be finite" % function)
+    if not np.all((sigma > 0) & np.isfinite(sigma)):
+        raise DomainError("%s: Scale parameter must be positive finite" % function)
+    if min(y.size, mu.size, sigma.size) == 0:
+        return 0.0, {}
+    n = max(y.size, mu.size, sigma.size)
+    for name, v in (("Random variable", y), ("Location parameter", mu), ("Scale parameter", sigma)):
+        if v.size != 1 and v.size != n:
+            raise ValueError("%s: %s has dimension = %d, expecting dimension = %d" % (function, name, v.size, n))
+    names = (("y", "dy", 1), ("mu", "dmu", 2), ("sigma", "dsigma", 4))
+    if propto and var_mask == 0:
+        if lognormal and np.any(y <= 0):
+            return -np.inf, {}
+        return 0.0, {}
+    flags = locscale_flags(density, propto, var_mask)
+    r = locscale_eval(density, y, mu, sigma, flags, y_is_data=y_is_data and not (var_mask & 1))
+    if r["rc"] == _abi.BAD_OPERAND:   # unreachable after the checks above; kept for symmetry with the C++ wrapper
+        raise DomainError("%s: operand outside the domain" % function)
+    if r["rc"] == _abi.LOG_ZERO:      # lognormal_lpdf.hpp:41-45: an outcome equal to zero, no partials
+        return -np.inf, {}
+    return r["lp"], {name: r[key] for name, key, bit in names if var_mask & bit}
+
+
+def locscale_flags(density, propto=False, var_mask=0b110):
+    """Which summands the reference keeps under include_summand<propto, ...> (normal_lpdf.hpp:89-97,
+    cauchy_lpdf.hpp:87-95, lognormal_lpdf.hpp:92-118) for the operands that are variables (var_mask bit 0: y, 1: mu,
+    2: sigma), and which partials they need."""
+    vy, vm, vs = bool(var_mask & 1), bool(var_mask & 2), bool(var_mask & 4)
+    f = (_abi.NEED_DY if vy else 0) | (_abi.NEED_DALPHA if vm else 0) | (_abi.NEED_DSIGMA if vs else 0)
+    if not propto:
+        f |= _abi.LP_CONST
+    if not propto or vs:
+        f |= _abi.LP_SCALE
+    if not propto or vy or vm or vs:
+        f |= _abi.LP_MAIN
+    if density in ("lognormal", _abi.LOCSCALE_LOGNORMAL) and (not propto or vy):
+        f |= _abi.LP_Y
+    return f
+
+
+def cauchy_lpdf(y, mu, sigma, propto=False, var_mask=0b110, y_is_data=True):
+    """stan/math/prim/scal/prob/cauchy_lpdf.hpp:35-37; var_mask: which of y (bit 0), mu (1), sigma (2) are variables;
+    grads: the partials of those."""
+    return _locscale_lpdf("cauchy_lpdf", "cauchy", y, mu, sigma, propto, var_mask, y_is_data)
+
+
+def lognormal_lpdf(y, mu, sigma, propto=False, var_mask=0b110, y_is_data=True):
+    """stan/math/prim/scal/prob/lognormal_lpdf.hpp:19-21; var_mask and grads as for cauchy_lpdf."""
+    return _locscale_lpdf("lognormal_lpdf", "lognormal", y, mu, sigma, propto, var_mask, y_is_data)
+
 def student_t_eval(y, nu, mu, sigma, flags, y_is_data=True):
     """One stan_cuda_student_t_lpdf_eval call; returns {"rc", "lp", "dy", "dnu", "dmu", "dsigma"} (partials for the
     NEED_* bits in flags, each the length of its operand)."""

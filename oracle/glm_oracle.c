@@ -361,6 +361,73 @@ int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a) {
   return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+/* cauchy_lpdf (stan/math/prim/scal/prob/cauchy_lpdf.hpp:35-113) and lognormal_lpdf
+ * (stan/math/prim/scal/prob/lognormal_lpdf.hpp:19-133) on the operands of normal_lpdf; density 0 is normal_lpdf
+ * itself with its eager checks (normal_lpdf.hpp:51-53) turned into BAD_OPERAND.  Scalar operands accumulate their
+ * partial over n (broadcast_array). */
+#define ORACLE_NEG_LOG_PI (-1.14472988584940017414342735135)
+int oracle_locscale_lpdf_eval(int density, const stan_cuda_normal_args* a) {
+  if (!a || a->n < 0 || density < STAN_CUDA_LOCSCALE_NORMAL || density > STAN_CUDA_LOCSCALE_LOGNORMAL) return STAN_CUDA_ERR_ARG;
+  if (a->n == 0) {
+    if (a->lp) *a->lp = 0.0;
+    return STAN_CUDA_OK;
+  }
+  const int lognormal = density == STAN_CUDA_LOCSCALE_LOGNORMAL, normal = density == STAN_CUDA_LOCSCALE_NORMAL;
+  for (int64_t i = 0; i < a->y_len; ++i)
+    if (isnan(a->y[i]) || (lognormal && a->y[i] < 0)) return STAN_CUDA_BAD_OPERAND;          /* cauchy :47, lognormal :24-25 */
+  for (int64_t i = 0; i < a->mu_len; ++i) if (!isfinite(a->mu[i])) return STAN_CUDA_BAD_OPERAND;            /* :48 / :26 */
+  for (int64_t i = 0; i < a->sigma_len; ++i)
+    if (!(a->sigma[i] > 0.0) || (!normal && !isfinite(a->sigma[i]))) return STAN_CUDA_BAD_OPERAND;          /* :49 / :27 */
+  if (normal) return oracle_normal_lpdf_eval(a);
+  if (lognormal)
+    for (int64_t i = 0; i < a->y_len; ++i)
+      if (a->y[i] <= 0) {                                                                                   /* :41-45 */
+        if (a->lp) *a->lp = -INFINITY;
+        return STAN_CUDA_LOG_ZERO;
+      }
+  const int ym = a->y_len != 1, mm = a->mu_len != 1, sm = a->sigma_len != 1;
+  const int need_mu = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dmu;
+  const int need_sigma = (a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma;
+  const int need_y = (a->flags & STAN_CUDA_NEED_DY) && a->dy;
+  if (need_mu) for (int64_t i = 0; i < a->mu_len; ++i) a->dmu[i] = 0.0;
+  if (need_sigma) for (int64_t i = 0; i < a->sigma_len; ++i) a->dsigma[i] = 0.0;
+  if (need_y) for (int64_t i = 0; i < a->y_len; ++i) a->dy[i] = 0.0;
+  double logp = 0.0;
+  if (lognormal && (a->flags & STAN_CUDA_LP_CONST)) logp += a->n * ORACLE_NEG_LOG_SQRT_TWO_PI;              /* :92-94 */
+  for (int64_t n = 0; n < a->n; ++n) {
+    const double y = a->y[ym ? n : 0], mu = a->mu[mm ? n : 0], sg = a->sigma[sm ? n : 0];
+    const double inv_sigma = 1.0 / sg;
+    if (!lognormal) {                                                                /* cauchy_lpdf.hpp:77-110 */
+      const double sigma_squared = sg * sg;
+      const double y_minus_mu = y - mu;
+      const double y_minus_mu_squared = y_minus_mu * y_minus_mu;
+      const double y_minus_mu_over_sigma = y_minus_mu * inv_sigma;
+      const double y_minus_mu_over_sigma_squared = y_minus_mu_over_sigma * y_minus_mu_over_sigma;
+      if (a->flags & STAN_CUDA_LP_CONST) logp += ORACLE_NEG_LOG_PI;
+      if (a->flags & STAN_CUDA_LP_SCALE) logp -= log(sg);
+      if (a->flags & STAN_CUDA_LP_MAIN) logp -= log1p(y_minus_mu_over_sigma_squared);
+      if (need_y) a->dy[ym ? n : 0] -= 2 * y_minus_mu / (sigma_squared + y_minus_mu_squared);
+      if (need_mu) a->dmu[mm ? n : 0] += 2 * y_minus_mu / (sigma_squared + y_minus_mu_squared);
+      if (need_sigma)
+        a->dsigma[sm ? n : 0] += (y_minus_mu_squared - sigma_squared) * inv_sigma / (sigma_squared + y_minus_mu_squared);
+    } else {                                                                         /* lognormal_lpdf.hpp:96-131 */
+      const double inv_sigma_sq = inv_sigma * inv_sigma;
+      const double log_y = log(y), inv_y = 1 / y;
+      const double logy_m_mu = log_y - mu;
+      const double logy_m_mu_sq = logy_m_mu * logy_m_mu;
+      const double logy_m_mu_div_sigma = logy_m_mu * inv_sigma_sq;
+      if (a->flags & STAN_CUDA_LP_SCALE) logp -= log(sg);
+      if (a->flags & STAN_CUDA_LP_Y) logp -= log_y;
+      if (a->flags & STAN_CUDA_LP_MAIN) logp -= 0.5 * logy_m_mu_sq * inv_sigma_sq;
+      if (need_y) a->dy[ym ? n : 0] -= (1 + logy_m_mu_div_sigma) * inv_y;
+      if (need_mu) a->dmu[mm ? n : 0] += logy_m_mu_div_sigma;
+      if (need_sigma) a->dsigma[sm ? n : 0] += (logy_m_mu_div_sigma * logy_m_mu - 1) * inv_sigma;
+    }
+  }
+  if (a->lp) *a->lp = logp;
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
 /* stan/math/prim/scal/prob/student_t_lpdf.hpp:55-201.  The eager checks (:67-70) become BAD_OPERAND; scalar
  * operands accumulate their partial over n (prim/scal/meta/broadcast_array.hpp:9-33). */
 #define ORACLE_NEG_LOG_SQRT_PI (-0.5723649429247000870717135)

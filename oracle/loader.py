@@ -39,6 +39,8 @@ def oracle_lib():
         lib.oracle_glm_eval.argtypes = [C.POINTER(_abi.GlmArgs)]
         lib.oracle_normal_lpdf_eval.restype = C.c_int
         lib.oracle_normal_lpdf_eval.argtypes = [C.POINTER(_abi.NormalArgs)]
+        lib.oracle_locscale_lpdf_eval.restype = C.c_int
+        lib.oracle_locscale_lpdf_eval.argtypes = [C.c_int, C.POINTER(_abi.NormalArgs)]
         lib.oracle_student_t_lpdf_eval.restype = C.c_int
         lib.oracle_student_t_lpdf_eval.argtypes = [C.POINTER(_abi.StudentTArgs)]
         i64, vp_ = C.c_int64, C.c_void_p
@@ -86,6 +88,9 @@ def ref_lib():
         if hasattr(lib, "stanref_density"):
             lib.stanref_density.restype = i
             lib.stanref_density.argtypes = [i, i, l, vp, l, dp, l, i, dp, dp, dp, C.c_char_p, i]
+        if hasattr(lib, "stanref_locscale_lpdf"):
+            lib.stanref_locscale_lpdf.restype = i
+            lib.stanref_locscale_lpdf.argtypes = [i, i, i, dp, l, dp, l, dp, l, dp, dp, dp, dp, dp, C.c_char_p, i]
         if hasattr(lib, "stanref_student_t_lpdf"):
             lib.stanref_student_t_lpdf.restype = i
             lib.stanref_student_t_lpdf.argtypes = [i, i, dp, l, dp, l, dp, l, dp, l, dp, dp, dp, dp, dp, dp,
@@ -373,6 +378,57 @@ def ref_normal_lpdf(y, mu, sigma, propto=False, need_dy=False):
     res = {"rc": 0, "lp": float(lp[0]), "dmu": dmu, "dsigma": dsigma, "seconds": float(secs[0])}
     if need_dy:
         res["dy"] = dy
+    return res
+
+
+# ------------------------------------------------------------------------------------------
+# normal_lpdf / cauchy_lpdf / lognormal_lpdf (y | mu, sigma).  var_mask bit 0: y, 1: mu, 2: sigma are autodiff variables.
+def locscale_flags(density, propto=False, var_mask=0b110):
+    """The summands the reference keeps under include_summand<propto, ...> (normal_lpdf.hpp:89-97, cauchy_lpdf.hpp:87-95,
+    lognormal_lpdf.hpp:92-118) and the partials of the operands that are variables."""
+    d = _abi.LOCSCALES[density] if isinstance(density, str) else density
+    vy, vm, vs = bool(var_mask & 1), bool(var_mask & 2), bool(var_mask & 4)
+    f = (_abi.NEED_DY if vy else 0) | (_abi.NEED_DALPHA if vm else 0) | (_abi.NEED_DSIGMA if vs else 0)
+    if not propto:
+        f |= _abi.LP_CONST
+    if not propto or vs:
+        f |= _abi.LP_SCALE
+    if not propto or vy or vm or vs:
+        f |= _abi.LP_MAIN
+    if d == _abi.LOCSCALE_LOGNORMAL and (not propto or vy):
+        f |= _abi.LP_Y
+    return f
+
+
+def oracle_locscale_lpdf(density, y, mu, sigma, propto=False, var_mask=0b110, flags=None):
+    d = _abi.LOCSCALES[density] if isinstance(density, str) else density
+    if flags is None:
+        flags = locscale_flags(d, propto, var_mask)
+    a, out, (y, mu, sigma) = normal_args(y, mu, sigma, flags)
+    rc = oracle_lib().oracle_locscale_lpdf_eval(d, C.byref(a))
+    res = {"rc": rc, "lp": float(out["lp"][0])}
+    for key, bit, op in (("dy", _abi.NEED_DY, y), ("dmu", _abi.NEED_DALPHA, mu), ("dsigma", _abi.NEED_DSIGMA, sigma)):
+        if flags & bit:
+            res[key] = out[key][:op.size].copy()
+    return res
+
+
+def ref_locscale_lpdf(density, y, mu, sigma, propto=False, var_mask=0b110):
+    """The compiled reference itself (oracle/ref_shim_locscale.cpp); raises RefError where it throws."""
+    d = _abi.LOCSCALES[density] if isinstance(density, str) else density
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    lp, secs = np.zeros(1), np.zeros(1)
+    dy, dmu, dsigma = np.zeros(max(y.size, 1)), np.zeros(max(mu.size, 1)), np.zeros(max(sigma.size, 1))
+    err = C.create_string_buffer(512)
+    rc = ref_lib().stanref_locscale_lpdf(d, int(propto), int(var_mask), y.ctypes.data, y.size, mu.ctypes.data, mu.size,
+                                         sigma.ctypes.data, sigma.size, lp.ctypes.data, dy.ctypes.data, dmu.ctypes.data,
+                                         dsigma.ctypes.data, secs.ctypes.data, err, 512)
+    if rc != 0:
+        raise RefError(rc, err.value.decode())
+    res = {"rc": 0, "lp": float(lp[0]), "seconds": float(secs[0])}
+    for key, bit, g, op in (("dy", 1, dy, y), ("dmu", 2, dmu, mu), ("dsigma", 4, dsigma, sigma)):
+        if var_mask & bit:
+            res[key] = g[:op.size].copy()
     return res
 
 

@@ -16,7 +16,9 @@
 #include <stan/math/cuda/ordered_logistic_glm_lpmf.hpp>
 #include <stan/math/cuda/categorical_logit_glm_lpmf.hpp>
 #include <stan/math/cuda/normal_lpdf.hpp>
+#include <stan/math/cuda/locscale_lpdf.hpp>
 #include <stan/math/cuda/student_t_lpdf.hpp>
+#include <stan/math/cuda/int_density.hpp>
 #include <stan/math/cuda/matrix_cuda.hpp>
 #include <stan/math/cuda/multiply.hpp>
 #include <stan/math/cuda/rev_multiply.hpp>

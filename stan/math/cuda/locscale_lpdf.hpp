@@ -1,0 +1,159 @@
+#ifndef STAN_MATH_CUDA_LOCSCALE_LPDF_HPP
+#define STAN_MATH_CUDA_LOCSCALE_LPDF_HPP
+#ifdef STAN_CUDA
+
+#include <stan/math/cuda/normal_lpdf.hpp>
+#include <stan/math/prim/scal/err/check_nonnegative.hpp>
+#include <stan/math/prim/scal/err/check_positive_finite.hpp>
+#include <stan/math/prim/scal/fun/constants.hpp>
+#include <stdexcept>
+#include <string>
+
+namespace stan {
+namespace math {
+namespace cuda {
+
+/**
+ * cauchy_lpdf and lognormal_lpdf on the device: the operands, their staging and the tape node are
+ * those of normal_lpdf_device (stan/math/cuda/normal_lpdf.hpp); the density id selects the per-element term of the
+ * kernel (stan_cuda_locscale_lpdf_eval).  Eligible calls: the vectorised ones with something to compute -- when
+ * include_summand<propto, T_y, T_loc, T_scale> is false the reference body only runs its checks, and stays in charge.
+ */
+template <bool propto, typename T_y, typename T_loc, typename T_scale>
+struct locscale_lpdf_eligible
+    : std::integral_constant<bool, normal_lpdf_eligible<T_y, T_loc, T_scale>::value
+                                       && include_summand<propto, T_y, T_loc, T_scale>::value> {};
+
+namespace detail {
+
+/** the eager checks of cauchy_lpdf.hpp:47-49, in the reference's order */
+struct cauchy_checks {
+  static const char* function() { return "cauchy_lpdf"; }
+  template <typename T_y, typename T_loc, typename T_scale>
+  static void run(const T_y& y, const T_loc& mu, const T_scale& sigma) {
+    check_not_nan(function(), "Random variable", y);
+    check_finite(function(), "Location parameter", mu);
+    check_positive_finite(function(), "Scale parameter", sigma);
+  }
+};
+/** the eager checks of lognormal_lpdf.hpp:24-27 */
+struct lognormal_checks {
+  static const char* function() { return "lognormal_lpdf"; }
+  template <typename T_y, typename T_loc, typename T_scale>
+  static void run(const T_y& y, const T_loc& mu, const T_scale& sigma) {
+    check_not_nan(function(), "Random variable", y);
+    check_nonnegative(function(), "Random variable", y);
+    check_finite(function(), "Location parameter", mu);
+    check_positive_finite(function(), "Scale parameter", sigma);
+  }
+};
+
+/**
+ * One vectorised evaluation: stages the operands, builds the tape node in place (arena_partials), calls the device.
+ * extra_flags: summand bits beyond the ones every location-scale density shares (lognormal: STAN_CUDA_LP_Y).
+ */
+template <bool propto, typename Checks, typename T_y, typename T_loc, typename T_scale>
+return_type_t<T_y, T_loc, T_scale> locscale_lpdf_call(int density, uint32_t extra_flags, const T_y& y, const T_loc& mu,
+                                                      const T_scale& sigma) {
+  const char* function = Checks::function();
+  // the reference reports a domain error before a size error: if the sizes disagree, its checks run in its order
+  const size_t N = max_size(y, mu, sigma);
+  if ((is_vector<T_y>::value && length(y) != N) || (is_vector<T_loc>::value && length(mu) != N)
+      || (is_vector<T_scale>::value && length(sigma) != N)) {
+    Checks::run(y, mu, sigma);
+    check_consistent_sizes(function, "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
+  }
+  const size_t by = staged_operand<T_y>::bytes(y), bm = staged_operand<T_loc>::bytes(mu),
+               bs = staged_operand<T_scale>::bytes(sigma);
+  double* stage = nullptr;
+  if (by + bm + bs > 0) {
+    stage = static_cast<double*>(stan_cuda_host_staging(by + bm + bs));
+    if (!stage) {
+      check_cuda_rc(function, STAN_CUDA_ERR_CUDA);
+    }
+  }
+  double* const stage_y = stage;
+  double* const stage_mu = stage ? stage + by / sizeof(double) : nullptr;
+  double* const stage_sigma = stage ? stage + (by + bm) / sizeof(double) : nullptr;
+  double* const sinks[5] = {gathered_by_node<T_y>::value ? stage_y : nullptr, gathered_by_node<T_loc>::value ? stage_mu : nullptr,
+                            gathered_by_node<T_scale>::value ? stage_sigma : nullptr, nullptr, nullptr};
+  arena_partials<T_y, T_loc, T_scale> ops_partials(y, mu, sigma, double(), double(), sinks);
+  double logp = 0;
+  stan_cuda_normal_args a = stan_cuda_normal_args();
+  a.n = N;
+  a.y = gathered_by_node<T_y>::value ? stage_y : staged_operand<T_y>::fill(y, stage_y);
+  a.y_len = length(y);
+  a.y_is_data = (is_constant_all<T_y>::value && staged_operand<T_y>::borrowed) ? 1 : 0;
+  a.mu = gathered_by_node<T_loc>::value ? stage_mu : staged_operand<T_loc>::fill(mu, stage_mu);
+  a.mu_len = length(mu);
+  a.sigma = gathered_by_node<T_scale>::value ? stage_sigma : staged_operand<T_scale>::fill(sigma, stage_sigma);
+  a.sigma_len = length(sigma);
+  a.lp = &logp;
+  a.flags = STAN_CUDA_LP_MAIN | extra_flags;
+  if (include_summand<propto>::value) {
+    a.flags |= STAN_CUDA_LP_CONST;
+  }
+  if (include_summand<propto, T_scale>::value) {
+    a.flags |= STAN_CUDA_LP_SCALE;
+  }
+  if (!is_constant_all<T_y>::value) {
+    a.flags |= STAN_CUDA_NEED_DY;
+    a.dy = ops_partials.partials(0);
+  }
+  if (!is_constant_all<T_loc>::value) {
+    a.flags |= STAN_CUDA_NEED_DALPHA;
+    a.dmu = ops_partials.partials(1);
+  }
+  if (!is_constant_all<T_scale>::value) {
+    a.flags |= STAN_CUDA_NEED_DSIGMA;
+    a.dsigma = ops_partials.partials(2);
+  }
+  const int rc = stan_cuda_locscale_lpdf_eval(density, &a);
+  check_cuda_rc(function, rc);
+  if (rc == STAN_CUDA_BAD_OPERAND) {
+    Checks::run(y, mu, sigma);
+    throw std::domain_error(std::string(function) + ": operand outside the domain (device check)");
+  }
+  if (rc == STAN_CUDA_LOG_ZERO) {
+    return LOG_ZERO;
+  }
+  return ops_partials.build(logp);
+}
+
+}  // namespace detail
+
+/**
+ * GPU body of the vectorised cauchy_lpdf (reference: stan/math/prim/scal/prob/cauchy_lpdf.hpp:35-113): the loop :77-110
+ * becomes one kernel; the eager checks :47-49 are answered by the same kernel (STAN_CUDA_BAD_OPERAND), after which the
+ * reference's check functions run on the host only to throw the identical exception.
+ */
+template <bool propto, typename T_y, typename T_loc, typename T_scale>
+return_type_t<T_y, T_loc, T_scale> cauchy_lpdf_device(const T_y& y, const T_loc& mu, const T_scale& sigma) {
+  if (size_zero(y, mu, sigma)) {
+    return 0.0;
+  }
+  return detail::locscale_lpdf_call<propto, detail::cauchy_checks>(STAN_CUDA_LOCSCALE_CAUCHY, 0u, y, mu, sigma);
+}
+
+/**
+ * GPU body of the vectorised lognormal_lpdf (reference: stan/math/prim/scal/prob/lognormal_lpdf.hpp:19-133): the loops
+ * :41-131 become one kernel, including the LOG_ZERO scan of the outcomes :41-45 (STAN_CUDA_LOG_ZERO) and the -log(y)
+ * summand the reference ties to include_summand<propto, T_y> (:113-115, STAN_CUDA_LP_Y).  The reference runs its checks
+ * before it looks at the sizes (:24-31): with an empty operand they have nothing to reject.
+ */
+template <bool propto, typename T_y, typename T_loc, typename T_scale>
+return_type_t<T_y, T_loc, T_scale> lognormal_lpdf_device(const T_y& y, const T_loc& mu, const T_scale& sigma) {
+  if (size_zero(y, mu, sigma)) {
+    detail::lognormal_checks::run(y, mu, sigma);
+    check_consistent_sizes("lognormal_lpdf", "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
+    return 0.0;
+  }
+  return detail::locscale_lpdf_call<propto, detail::lognormal_checks>(
+      STAN_CUDA_LOCSCALE_LOGNORMAL, include_summand<propto, T_y>::value ? STAN_CUDA_LP_Y : 0u, y, mu, sigma);
+}
+
+}  // namespace cuda
+}  // namespace math
+}  // namespace stan
+#endif
+#endif

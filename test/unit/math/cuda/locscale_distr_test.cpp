@@ -1,0 +1,50 @@
+// The reference's distribution-test fixture (test/prob/test_fixture_distr.hpp) and its cauchy and lognormal test
+// classes (test/prob/cauchy/cauchy_test.hpp, test/prob/lognormal/lognormal_test.hpp: known answers, invalid values),
+// all included UNMODIFIED from the reference tree and instantiated -- the way the reference's generator
+// (test/prob/generate_tests.cpp:235-340) writes its "_v_" files -- for argument kinds the overlay routes to the
+// B200 kernel (at least one container operand of double / var) plus one all-scalar kind that stays on the
+// reference loop.  Known answers, invalid values, propto behaviour, finite-difference and hand-written-function
+// gradients, vector-vs-repeated-scalar consistency: the fixture's own checks.
+#ifdef STAN_CUDA
+#include <gtest/gtest.h>
+#include <boost/mpl/vector.hpp>
+#include <test/prob/test_fixture_distr.hpp>
+#include <test/prob/cauchy/cauchy_test.hpp>
+#include <test/prob/lognormal/lognormal_test.hpp>
+#include <vector>
+
+typedef Eigen::Matrix<var, Eigen::Dynamic, 1> vector_var;
+typedef Eigen::Matrix<var, 1, Eigen::Dynamic> row_vector_var;
+typedef Eigen::Matrix<double, Eigen::Dynamic, 1> vector_dbl;
+
+// the model statement's kinds: double y vector, var vector mu, var scalar sigma
+typedef boost::mpl::vector<std::vector<double>, std::vector<var>, var, empty, empty, empty> type_v_0;
+typedef boost::mpl::vector<vector_dbl, vector_var, var, empty, empty, empty> type_v_1;
+typedef boost::mpl::vector<std::vector<var>, std::vector<var>, std::vector<var>, empty, empty, empty> type_v_2;
+typedef boost::mpl::vector<vector_var, double, vector_var, empty, empty, empty> type_v_3;
+typedef boost::mpl::vector<double, row_vector_var, double, empty, empty, empty> type_v_4;
+typedef boost::mpl::vector<std::vector<double>, var, std::vector<var>, empty, empty, empty> type_v_5;
+typedef boost::mpl::vector<var, vector_dbl, var, empty, empty, empty> type_v_6;
+typedef boost::mpl::vector<var, var, var, empty, empty, empty> type_v_7;  // all scalars: reference loop
+
+#define STAN_CUDA_DISTR(TEST_CLASS, N)                                                      \
+  typedef boost::mpl::vector<TEST_CLASS, type_v_##N> TEST_CLASS##_v_##N;                    \
+  INSTANTIATE_TYPED_TEST_CASE_P(TEST_CLASS##_v_##N, AgradDistributionTestFixture, TEST_CLASS##_v_##N);
+
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 0)
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 1)
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 2)
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 3)
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 4)
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 5)
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 6)
+STAN_CUDA_DISTR(AgradDistributionsCauchy, 7)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 0)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 1)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 2)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 3)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 4)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 5)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 6)
+STAN_CUDA_DISTR(AgradDistributionsLognormal, 7)
+#endif

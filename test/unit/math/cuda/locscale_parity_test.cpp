@@ -1,0 +1,200 @@
+// cauchy_lpdf / lognormal_lpdf on the device through the reference's own C++ signatures, against the
+// unmodified reference bodies (reachable in the same binary as *_reference_cpu, see overlay/), at the north star's
+// tolerance: every mix of var / double and vector / scalar operands that the overlay routes, propto on and off, the
+// reference's exceptions and its LOG_ZERO.
+#ifdef STAN_CUDA
+#include <stan/math.hpp>
+#include <gtest/gtest.h>
+#include <random>
+#include <string>
+#include <vector>
+
+using Eigen::Dynamic;
+using Eigen::Matrix;
+using Eigen::VectorXd;
+using stan::math::var;
+typedef Matrix<var, Dynamic, 1> vector_v;
+
+namespace {
+
+void expect_rel(double got, double ref, double scale, const char* what) {
+  const double denom = std::max(std::fabs(ref), 1e-8 * scale);
+  if (denom == 0) {
+    EXPECT_EQ(got, ref) << what;
+  } else {
+    EXPECT_LE(std::fabs(got - ref) / denom, 1e-10) << what << " got " << got << " ref " << ref;
+  }
+}
+void expect_vec(const VectorXd& got, const VectorXd& ref, const char* what) {
+  ASSERT_EQ(got.size(), ref.size()) << what;
+  const double scale = ref.size() ? ref.cwiseAbs().maxCoeff() : 0.0;
+  for (int i = 0; i < ref.size(); ++i) expect_rel(got[i], ref[i], scale, what);
+}
+VectorXd adj(const vector_v& v) {
+  VectorXd a(v.size());
+  for (int i = 0; i < v.size(); ++i) a[i] = v[i].adj();
+  return a;
+}
+VectorXd adj(const var& v) { return VectorXd::Constant(1, v.adj()); }
+vector_v to_v(const VectorXd& d) {
+  vector_v v(d.size());
+  for (int i = 0; i < d.size(); ++i) v[i] = d[i];
+  return v;
+}
+
+struct Data {
+  VectorXd y, y_pos, mu, sigma;
+};
+Data make(int n, unsigned seed) {
+  std::mt19937_64 rng(seed);
+  std::normal_distribution<double> nd(0, 1);
+  std::uniform_real_distribution<double> ud(0.3, 3.0);
+  Data d;
+  d.y.resize(n), d.y_pos.resize(n), d.mu.resize(n), d.sigma.resize(n);
+  for (int i = 0; i < n; ++i) {
+    d.y[i] = 2.0 * nd(rng);
+    d.y_pos[i] = std::exp(1.5 * nd(rng));
+    d.mu[i] = 0.7 * nd(rng);
+    d.sigma[i] = ud(rng);
+  }
+  return d;
+}
+
+}  // namespace
+
+#define STAN_CUDA_PARITY(NAME, GPU_CALL, CPU_CALL, ...)                                     \
+  {                                                                                         \
+    var lp_gpu = GPU_CALL;                                                                  \
+    lp_gpu.grad();                                                                          \
+    const double v_gpu = lp_gpu.val();                                                      \
+    std::vector<VectorXd> g_gpu = {__VA_ARGS__};                                            \
+    stan::math::set_zero_all_adjoints();                                                    \
+    var lp_cpu = CPU_CALL;                                                                  \
+    lp_cpu.grad();                                                                          \
+    std::vector<VectorXd> g_cpu = {__VA_ARGS__};                                            \
+    expect_rel(v_gpu, lp_cpu.val(), std::fabs(lp_cpu.val()), NAME " value");                \
+    for (size_t q = 0; q < g_cpu.size(); ++q) expect_vec(g_gpu[q], g_cpu[q], NAME " grad"); \
+    stan::math::set_zero_all_adjoints();                                                    \
+  }
+
+class CudaLocScale : public ::testing::TestWithParam<int> {};
+
+TEST_P(CudaLocScale, cauchy_matches_reference_loop) {
+  const int n = GetParam();
+  Data d = make(n, 100 + n);
+  vector_v y = to_v(d.y), mu = to_v(d.mu), sigma = to_v(d.sigma);
+  var mu0 = 0.2, sigma0 = 1.3;
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("cauchy, all var vectors", cauchy_lpdf(y, mu, sigma), cauchy_lpdf_reference_cpu<false>(y, mu, sigma), adj(y),
+                   adj(mu), adj(sigma));
+  STAN_CUDA_PARITY("cauchy, the model statement", cauchy_lpdf(d.y, mu, sigma0), cauchy_lpdf_reference_cpu<false>(d.y, mu, sigma0),
+                   adj(mu), adj(sigma0));
+  STAN_CUDA_PARITY("cauchy propto, data y", cauchy_lpdf<true>(d.y, mu, sigma0), cauchy_lpdf_reference_cpu<true>(d.y, mu, sigma0),
+                   adj(mu), adj(sigma0));
+  STAN_CUDA_PARITY("cauchy propto, data sigma", cauchy_lpdf<true>(d.y, mu, d.sigma), cauchy_lpdf_reference_cpu<true>(d.y, mu, d.sigma),
+                   adj(mu));
+  STAN_CUDA_PARITY("cauchy, scalar location", cauchy_lpdf(y, mu0, d.sigma), cauchy_lpdf_reference_cpu<false>(y, mu0, d.sigma), adj(y),
+                   adj(mu0));
+  const double v = cauchy_lpdf(d.y, d.mu, d.sigma);
+  expect_rel(v, cauchy_lpdf_reference_cpu<false>(d.y, d.mu, d.sigma), std::fabs(v), "cauchy, all double");
+  EXPECT_EQ(0.0, cauchy_lpdf<true>(d.y, d.mu, d.sigma));  // nothing to compute: the reference body
+  stan::math::recover_memory();
+}
+
+TEST_P(CudaLocScale, lognormal_matches_reference_loop) {
+  const int n = GetParam();
+  Data d = make(n, 200 + n);
+  vector_v y = to_v(d.y_pos), mu = to_v(d.mu), sigma = to_v(d.sigma);
+  var mu0 = 0.2, sigma0 = 1.3;
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("lognormal, all var vectors", lognormal_lpdf(y, mu, sigma), lognormal_lpdf_reference_cpu<false>(y, mu, sigma),
+                   adj(y), adj(mu), adj(sigma));
+  STAN_CUDA_PARITY("lognormal, the model statement", lognormal_lpdf(d.y_pos, mu, sigma0),
+                   lognormal_lpdf_reference_cpu<false>(d.y_pos, mu, sigma0), adj(mu), adj(sigma0));
+  STAN_CUDA_PARITY("lognormal propto, data y", lognormal_lpdf<true>(d.y_pos, mu, sigma0),
+                   lognormal_lpdf_reference_cpu<true>(d.y_pos, mu, sigma0), adj(mu), adj(sigma0));
+  STAN_CUDA_PARITY("lognormal propto, var y only", lognormal_lpdf<true>(y, d.mu, d.sigma),
+                   lognormal_lpdf_reference_cpu<true>(y, d.mu, d.sigma), adj(y));
+  STAN_CUDA_PARITY("lognormal, scalar location", lognormal_lpdf(y, mu0, d.sigma), lognormal_lpdf_reference_cpu<false>(y, mu0, d.sigma),
+                   adj(y), adj(mu0));
+  const double v = lognormal_lpdf(d.y_pos, d.mu, d.sigma);
+  expect_rel(v, lognormal_lpdf_reference_cpu<false>(d.y_pos, d.mu, d.sigma), std::fabs(v), "lognormal, all double");
+  EXPECT_EQ(0.0, lognormal_lpdf<true>(d.y_pos, d.mu, d.sigma));
+  stan::math::recover_memory();
+}
+
+INSTANTIATE_TEST_CASE_P(Sizes, CudaLocScale, ::testing::Values(1, 3, 1000, 100003));
+
+TEST(CudaLocScaleErrors, same_exceptions_and_log_zero_as_the_reference) {
+  using namespace stan::math;  // NOLINT
+  const int n = 2000;
+  Data d = make(n, 7);
+  vector_v mu = to_v(d.mu), sigma = to_v(d.sigma);
+  VectorXd y_nan = d.y, y_neg = d.y_pos, y_zero = d.y_pos;
+  y_nan[1999] = NAN;
+  y_neg[5] = -0.5;
+  y_zero[5] = 0.0;
+  vector_v mu_inf = to_v(d.mu), sigma_zero = to_v(d.sigma), sigma_inf = to_v(d.sigma);
+  mu_inf[17] = INFINITY;
+  sigma_zero[9] = 0.0;
+  sigma_inf[9] = INFINITY;
+  EXPECT_THROW(cauchy_lpdf(y_nan, mu, sigma), std::domain_error);
+  EXPECT_THROW(cauchy_lpdf(d.y, mu_inf, sigma), std::domain_error);
+  EXPECT_THROW(cauchy_lpdf(d.y, mu, sigma_zero), std::domain_error);
+  EXPECT_THROW(cauchy_lpdf(d.y, mu, sigma_inf), std::domain_error);
+  EXPECT_THROW(lognormal_lpdf(y_nan, mu, sigma), std::domain_error);
+  EXPECT_THROW(lognormal_lpdf(y_neg, mu, sigma), std::domain_error);
+  EXPECT_THROW(lognormal_lpdf(d.y_pos, mu_inf, sigma), std::domain_error);
+  EXPECT_THROW(lognormal_lpdf(d.y_pos, mu, sigma_inf), std::domain_error);
+  vector_v shorter = to_v(d.mu.head(n - 1));
+  EXPECT_THROW(cauchy_lpdf(d.y, shorter, sigma), std::invalid_argument);
+  EXPECT_THROW(lognormal_lpdf(d.y_pos, shorter, sigma), std::invalid_argument);
+  std::string m_gpu, m_cpu;
+  try {
+    cauchy_lpdf(d.y, mu, sigma_inf);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    cauchy_lpdf_reference_cpu<false>(d.y, mu, sigma_inf);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  m_gpu.clear();
+  m_cpu.clear();
+  try {
+    lognormal_lpdf(y_neg, mu, sigma);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    lognormal_lpdf_reference_cpu<false>(y_neg, mu, sigma);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  // an outcome equal to zero: LOG_ZERO (lognormal_lpdf.hpp:41-45)
+  EXPECT_EQ(LOG_ZERO, lognormal_lpdf(y_zero, mu, sigma).val());
+  EXPECT_EQ(LOG_ZERO, lognormal_lpdf_reference_cpu<false>(y_zero, mu, sigma).val());
+  VectorXd none(0);
+  vector_v empty(0);
+  EXPECT_EQ(0.0, cauchy_lpdf(none, empty, empty).val());
+  EXPECT_EQ(0.0, lognormal_lpdf(none, empty, empty).val());
+  stan::math::recover_memory();
+}
+
+TEST(CudaLocScaleRouting, the_device_is_used) {
+  stan_cuda_stats_t s0, s1;
+  Data d = make(5000, 3);
+  vector_v mu = to_v(d.mu);
+  stan_cuda_stats(&s0);
+  var lp = stan::math::cauchy_lpdf(d.y, mu, 1.5) + stan::math::lognormal_lpdf(d.y_pos, mu, 1.5);
+  stan_cuda_stats(&s1);
+  EXPECT_GE(s1.evals + s1.kernel_launches, s0.evals + s0.kernel_launches + 2);
+  EXPECT_TRUE(std::isfinite(lp.val()));
+  stan::math::recover_memory();
+}
+#endif

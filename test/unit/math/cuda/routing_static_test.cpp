@@ -65,6 +65,13 @@ static_assert(cu::student_t_lpdf_eligible<vector_v, vector_v, vector_v, vector_v
 static_assert(cu::student_t_lpdf_eligible<double, double, vector_d, double>::value, "all data");
 static_assert(!cu::student_t_lpdf_eligible<double, var, var, var>::value, "scalar call stays on the reference loops");
 static_assert(!cu::student_t_lpdf_eligible<vector_d, vector_fd, double, double>::value, "fvar");
+// vectorised cauchy_lpdf / lognormal_lpdf: the operand kinds of normal_lpdf, and something to compute
+static_assert(cu::locscale_lpdf_eligible<false, vector_d, vector_v, var>::value, "the model statement");
+static_assert(cu::locscale_lpdf_eligible<true, vector_d, vector_v, var>::value, "propto with variables");
+static_assert(cu::locscale_lpdf_eligible<false, vector_d, vector_d, double>::value, "all data, not propto");
+static_assert(!cu::locscale_lpdf_eligible<true, vector_d, vector_d, double>::value, "propto, all data: only the reference's checks run");
+static_assert(!cu::locscale_lpdf_eligible<false, double, var, var>::value, "scalar call stays on the reference loop");
+static_assert(!cu::locscale_lpdf_eligible<false, vector_d, vector_fd, double>::value, "fvar");
 // vectorised bernoulli_logit_lpmf / poisson_log_lpmf / poisson_lpmf / bernoulli_lpmf: container operand of double / var
 static_assert(cu::int_density_eligible<ints, vector_v>::value, "d1 signature");
 static_assert(cu::int_density_eligible<int, std::vector<var>>::value, "scalar n");
@@ -82,6 +89,9 @@ static_assert(std::is_same<decltype(stan::math::normal_lpdf(vector_d(), vector_v
 static_assert(std::is_same<decltype(stan::math::bernoulli_logit_lpmf(ints(), vector_d())), double>::value, "");
 static_assert(std::is_same<decltype(stan::math::poisson_log_lpmf(ints(), vector_fd())), fvar<double>>::value, "");
 static_assert(std::is_same<decltype(stan::math::poisson_lpmf(ints(), vector_v())), var>::value, "");
+static_assert(std::is_same<decltype(stan::math::cauchy_lpdf(vector_d(), vector_v(), 1.0)), var>::value, "");
+static_assert(std::is_same<decltype(stan::math::lognormal_lpdf<true>(vector_d(), vector_d(), 1.0)), double>::value, "");
+static_assert(std::is_same<decltype(stan::math::lognormal_lpdf(vector_d(), vector_fd(), 1.0)), fvar<double>>::value, "");
 static_assert(std::is_same<decltype(stan::math::poisson_lpmf<true>(ints(), vector_d())), double>::value, "");
 static_assert(std::is_same<decltype(stan::math::bernoulli_lpmf(ints(), vector_fd())), fvar<double>>::value, "");
 static_assert(std::is_same<decltype(stan::math::bernoulli_lpmf(1, std::vector<var>())), var>::value, "");

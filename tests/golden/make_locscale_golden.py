@@ -1,0 +1,67 @@
+"""Generates tests/golden/locscale_golden.npz from the UNMODIFIED reference (oracle/_ref/libstanref.so, compiled from
+/root/reference by oracle/Makefile): cauchy_lpdf(y | mu, sigma) and lognormal_lpdf(y | mu, sigma), value + reverse-mode
+gradient, for
+  * the reference's known-answer triples (test/prob/cauchy/cauchy_test.hpp:10-31,
+    test/prob/lognormal/lognormal_test.hpp:10-25; the literal expected log-densities stored beside the output),
+  * every subset of {y, mu, sigma} as autodiff variables x propto on one seeded vector case (the summands the
+    reference drops under propto depend on which operands are variables, cauchy_lpdf.hpp:87-95,
+    lognormal_lpdf.hpp:92-118),
+  * every mix of scalar / vector operands,
+  * the corners: outcomes far in the tails, tiny and huge scales, lognormal outcomes from 1e-300 to 1e300.
+Run here (the container with /root/reference):  python tests/golden/make_locscale_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import loader as L  # noqa: E402
+
+out, names = {}, []
+
+
+def add(name, density, y, mu, sigma, propto=False, var_mask=0b110, known_answer=None):
+    p = "ls/%s/" % name
+    r = L.ref_locscale_lpdf(density, y, mu, sigma, propto=propto, var_mask=var_mask)
+    out[p + "density"] = np.array(L._abi.LOCSCALES[density])
+    for key, v in (("y", y), ("mu", mu), ("sigma", sigma)):
+        out[p + key] = np.asarray(v, float).reshape(-1)
+    out[p + "propto"], out[p + "var_mask"], out[p + "lp"] = np.array(int(propto)), np.array(int(var_mask)), np.array(r["lp"])
+    for key in ("dy", "dmu", "dsigma"):
+        if key in r:
+            out[p + key] = np.asarray(r[key], float)
+    if known_answer is not None:
+        out[p + "known_answer"] = np.array(known_answer)
+    names.append(name)
+
+
+for i, (y, mu, sg, ka) in enumerate([(1.0, 0.0, 1.0, -1.837877066409345339082), (-1.5, 0.0, 1.0, -2.323384882191046330036),
+                                     (-1.5, -1.0, 1.0, -1.367873437163609873224)]):
+    add("cauchy_ka%d" % i, "cauchy", [y], [mu], [sg], var_mask=0b111, known_answer=ka)
+for i, (y, mu, sg, ka) in enumerate([(1.2, 0.3, 1.5, -1.509802579439102343528), (12.0, 3.0, 0.9, -3.462263160811773765602)]):
+    add("lognormal_ka%d" % i, "lognormal", [y], [mu], [sg], var_mask=0b111, known_answer=ka)
+
+rng = np.random.default_rng(20191110)
+n = 400
+z = np.concatenate([rng.standard_normal(n) * 2.0, [1e3, -1e3, 1e8, -1e-8, 0.0, 300.0]])
+mu = np.concatenate([rng.standard_normal(n) * 0.7, [0.5, -0.5, 1.0, 0.0, 0.0, -300.0]])
+sg = np.concatenate([rng.uniform(0.3, 3.0, n), [1e-3, 1e3, 2.0, 1e-8, 1e8, 0.7]])
+yl = np.concatenate([np.exp(rng.standard_normal(n) * 1.5), [1e-300, 1e300, 1.0, 1e-8, 1e8, 5.0]])
+mul = np.concatenate([rng.standard_normal(n) * 0.7, [-600.0, 600.0, 0.0, -10.0, 10.0, 1.0]])
+for density, yy, mm in (("cauchy", z, mu), ("lognormal", yl, mul)):
+    for var_mask in range(8):
+        for propto in (False, True):
+            add("%s_vec_m%d%s" % (density, var_mask, "_propto" if propto else ""), density, yy, mm, sg, propto=propto,
+                var_mask=var_mask)
+    # (scalar operands against the seeded part only: next to the corner entries they overflow the partials)
+    add(density + "_scalar_mu_sigma", density, yy[:n], [0.2], [1.3], var_mask=0b111)
+    add(density + "_scalar_y", density, yy[:1] if density == "cauchy" else [2.5], mm[:n], sg[:n], var_mask=0b111)
+    add(density + "_scalar_sigma", density, yy[:n], mm[:n], [0.8], var_mask=0b110)
+    add(density + "_scalar_mu", density, yy[:n], [-0.4], sg[:n], var_mask=0b011)
+
+out["cases"] = np.array(names)
+path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "locscale_golden.npz")
+np.savez_compressed(path, **out)
+print("wrote", path, len(names), "cases,", os.path.getsize(path), "bytes")

@@ -162,6 +162,14 @@ int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a) {
   return rc < 0 ? fail(rc, "stan_cuda_normal_lpdf_eval: bad argument") : rc;
 }
 
+int oracle_locscale_lpdf_eval(int density, const stan_cuda_normal_args* a);
+int stan_cuda_locscale_lpdf_eval(int32_t density, const stan_cuda_normal_args* a) {
+  if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_locscale_lpdf_eval: null args");
+  __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);
+  TIMED(oracle_locscale_lpdf_eval(density, a)); /* code 3 / LOG_ZERO as the header describes */
+  return rc < 0 ? fail(rc, "stan_cuda_locscale_lpdf_eval: bad argument") : rc;
+}
+
 int stan_cuda_student_t_lpdf_eval(const stan_cuda_student_t_args* a) {
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_student_t_lpdf_eval: null args");
   __atomic_fetch_add(&g_evals, 1, __ATOMIC_RELAXED);

@@ -1,0 +1,183 @@
+"""cauchy_lpdf / lognormal_lpdf (and normal_lpdf through the same entry point) on the device
+(stan_cuda_locscale_lpdf_eval, csrc/normal_lpdf.cu): the plain-C oracle against the golden vectors of the compiled
+reference (CPU), and the CUDA path against both (GPU).  Bar: 1e-10 relative on the log-density and on every partial."""
+import numpy as np
+import pytest
+
+from math_b200 import _abi
+from oracle import loader as L
+from tests.helpers import assert_close
+
+needs_ref = pytest.mark.skipif(not L.have_ref(), reason="oracle/_ref/libstanref.so not built")
+KEYS = (("dy", 1), ("dmu", 2), ("dsigma", 4))
+
+
+@pytest.fixture(scope="module")
+def golden_ls():
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    return np.load(os.path.join(root, "tests", "golden", "locscale_golden.npz"), allow_pickle=False)
+
+
+def ls_case(g, name):
+    p = "ls/%s/" % name
+    c = {k: g[p + k] for k in ("y", "mu", "sigma")}
+    c["density"], c["propto"], c["var_mask"] = int(g[p + "density"]), bool(g[p + "propto"]), int(g[p + "var_mask"])
+    c["lp"] = float(g[p + "lp"])
+    for k, _ in KEYS:
+        if p + k in g.files:
+            c[k] = g[p + k]
+    if p + "known_answer" in g.files:
+        c["known_answer"] = float(g[p + "known_answer"])
+    return c
+
+
+def check_case(r, c, what, rtol=1e-10):
+    assert r["rc"] == 0, what
+    assert_close(r["lp"], c["lp"], what + " lp", rtol)
+    for k, bit in KEYS:
+        if c["var_mask"] & bit:
+            assert_close(r[k], c[k], what + " " + k, rtol)
+            # element by element: relative to the element, floored at 1e-8 of the largest one
+            ref, got = np.asarray(c[k], float), np.asarray(r[k], float)
+            err = np.abs(got - ref) / np.maximum(np.abs(ref), 1e-8 * max(np.max(np.abs(ref)), 1e-300))
+            assert not (err > rtol).any(), "%s %s: %d components off, worst %.3e" % (what, k, int((err > rtol).sum()), err.max())
+        else:
+            assert k not in r
+
+
+def test_oracle_matches_golden_and_known_answers(golden_ls):
+    """outputs of the compiled reference and the literal expected values of test/prob/cauchy/cauchy_test.hpp:10-31,
+    test/prob/lognormal/lognormal_test.hpp:10-25"""
+    assert len(golden_ls["cases"]) >= 45
+    known = 0
+    for name in golden_ls["cases"]:
+        c = ls_case(golden_ls, str(name))
+        r = L.oracle_locscale_lpdf(c["density"], c["y"], c["mu"], c["sigma"], propto=c["propto"], var_mask=c["var_mask"])
+        check_case(r, c, "oracle vs golden " + str(name), rtol=1e-12)
+        if "known_answer" in c:
+            known += 1
+            assert abs(r["lp"] - c["known_answer"]) <= 1e-13 * max(1.0, abs(c["known_answer"])), name
+    assert known == 5
+
+
+def test_oracle_codes():
+    """BAD_OPERAND where the reference throws (cauchy_lpdf.hpp:47-49, lognormal_lpdf.hpp:24-27; the invalid values of the
+    reference's fixtures: infinite location, zero / negative / infinite scale), LOG_ZERO for a lognormal outcome of zero."""
+    for d in ("cauchy", "lognormal"):
+        for mu in (np.inf, -np.inf, np.nan):
+            assert L.oracle_locscale_lpdf(d, [1.0], [mu], [1.0])["rc"] == _abi.BAD_OPERAND
+        for sg in (0.0, -1.0, np.inf, -np.inf, np.nan):
+            assert L.oracle_locscale_lpdf(d, [1.0], [0.0], [sg])["rc"] == _abi.BAD_OPERAND
+        assert L.oracle_locscale_lpdf(d, [np.nan], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
+        assert L.oracle_locscale_lpdf(d, [], [], [])["lp"] == 0.0
+    assert L.oracle_locscale_lpdf("lognormal", [-1.0], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
+    r = L.oracle_locscale_lpdf("lognormal", [1.0, 0.0], [0.0], [1.0])
+    assert r["rc"] == _abi.LOG_ZERO and r["lp"] == -np.inf
+    assert L.oracle_locscale_lpdf("cauchy", [np.inf], [0.0], [1.0])["rc"] == _abi.NONFINITE   # legal outcome, -inf density
+    assert L.oracle_locscale_lpdf("normal", [1.0], [0.0], [np.inf])["rc"] in (0, _abi.NONFINITE)   # check_positive only
+
+
+@needs_ref
+@pytest.mark.parametrize("density", ["normal", "cauchy", "lognormal"])
+def test_oracle_vs_compiled_reference(density):
+    rng = np.random.default_rng(5)
+    n = 3000
+    y = rng.standard_normal(n) * 2
+    y = np.exp(y) if density == "lognormal" else y
+    mu, sg = rng.standard_normal(n), rng.uniform(0.3, 3.0, n)
+    for var_mask in range(8):
+        for propto in (False, True):
+            for ops in ((y, mu, sg), (y, mu[:1], sg[:1]), (y[:1], mu, sg)):
+                ref = L.ref_locscale_lpdf(density, *ops, propto=propto, var_mask=var_mask)
+                got = L.oracle_locscale_lpdf(density, *ops, propto=propto, var_mask=var_mask)
+                assert got["rc"] == 0
+                assert_close(got["lp"], ref["lp"], "%s lp" % density, 1e-12)
+                for k, bit in KEYS:
+                    if var_mask & bit:
+                        assert_close(got[k], ref[k], "%s %s" % (density, k), 1e-12)
+
+
+# ---- the CUDA path -------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def glm():
+    from math_b200 import glm as g
+    g.init(1)
+    g.cache_clear()
+    yield g
+    g.cache_clear()
+
+
+@pytest.mark.gpu
+def test_device_matches_golden(glm, golden_ls):
+    by_id = {_abi.LOCSCALE_CAUCHY: glm.cauchy_lpdf, _abi.LOCSCALE_LOGNORMAL: glm.lognormal_lpdf}
+    for name in golden_ls["cases"]:
+        c = ls_case(golden_ls, str(name))
+        r = glm.locscale_eval(c["density"], c["y"], c["mu"], c["sigma"], glm.locscale_flags(c["density"], c["propto"], c["var_mask"]),
+                              y_is_data=not (c["var_mask"] & 1))
+        check_case(r, c, "cuda vs golden " + str(name))
+        if "known_answer" in c:
+            assert abs(r["lp"] - c["known_answer"]) <= 1e-12 * max(1.0, abs(c["known_answer"])), name
+        lp, g = by_id[c["density"]](c["y"], c["mu"], c["sigma"], propto=c["propto"], var_mask=c["var_mask"])
+        assert lp == r["lp"] or (c["propto"] and c["var_mask"] == 0 and lp == 0.0)
+        for (key, bit), gname in zip(KEYS, ("y", "mu", "sigma")):
+            if c["var_mask"] & bit:
+                assert np.array_equal(g[gname], r[key])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("density", ["normal", "cauchy", "lognormal"])
+@pytest.mark.parametrize("n", [1, 2, 31, 1025, 100_003, 1_000_000])
+def test_device_against_oracle(glm, density, n):
+    rng = np.random.default_rng(n + len(density))
+    y = rng.standard_normal(n) * 2
+    y = np.exp(y) if density == "lognormal" else y
+    mu, sg = rng.standard_normal(n), rng.uniform(0.3, 3.0, n)
+    for var_mask, propto in ((0b111, False), (0b110, True), (0b001, True), (0b000, False)):
+        flags = glm.locscale_flags(density, propto, var_mask)
+        ref = L.oracle_locscale_lpdf(density, y, mu, sg, flags=flags)
+        got = glm.locscale_eval(density, y, mu, sg, flags, y_is_data=not (var_mask & 1))
+        c = dict(ref, var_mask=var_mask)
+        check_case(got, c, "%s n=%d mask=%d propto=%d" % (density, n, var_mask, propto))
+    flags = glm.locscale_flags(density, False, 0b111)
+    first = glm.locscale_eval(density, y, mu, sg, flags, y_is_data=False)
+    again = glm.locscale_eval(density, y, mu, sg, flags, y_is_data=False)
+    assert first["lp"] == again["lp"] and all(np.array_equal(first[k], again[k]) for k, _ in KEYS)   # fixed summation order
+    # scalar operands: their partials are sums over the elements
+    for ops in ((y, mu[:1], sg[:1]), (y[:1], mu, sg), (y, mu, sg[:1])):
+        ref = L.oracle_locscale_lpdf(density, *ops, flags=flags)
+        got = glm.locscale_eval(density, *ops, flags, y_is_data=False)
+        check_case(got, dict(ref, var_mask=0b111), "%s scalar operands n=%d" % (density, n))
+
+
+@pytest.mark.gpu
+def test_device_error_contract(glm):
+    """cauchy_lpdf.hpp:42-58, lognormal_lpdf.hpp:24-45 and the invalid values of the reference's fixtures"""
+    n = 3000
+    y, mu, sg = np.linspace(0.1, 5, n), np.linspace(-1, 1, n), np.linspace(0.5, 2, n)
+    for d, f in (("cauchy", glm.cauchy_lpdf), ("lognormal", glm.lognormal_lpdf)):
+        for k, bad_value in ((1, np.inf), (1, -np.inf), (2, 0.0), (2, -1.0), (2, np.inf), (0, np.nan)):
+            ops = [y.copy(), mu.copy(), sg.copy()]
+            ops[k][1234] = bad_value
+            with pytest.raises(glm.DomainError):
+                f(*ops)
+            flags = glm.locscale_flags(d, False, 0b110)
+            # the kernel's own element test (y travels per call: a cached data vector is trusted by address + samples)
+            assert glm.locscale_eval(d, *ops, flags, y_is_data=False)["rc"] == _abi.BAD_OPERAND
+        with pytest.raises(ValueError) as e:
+            f(y[:10], mu[:9], sg[:10])
+        assert not isinstance(e.value, glm.DomainError)
+        assert f([], [], [])[0] == 0.0
+        assert f(y, mu, sg, propto=True, var_mask=0)[0] == 0.0
+    # lognormal: a negative outcome throws, an outcome of zero is LOG_ZERO without partials
+    yn = y.copy()
+    yn[7] = -0.5
+    with pytest.raises(glm.DomainError):
+        glm.lognormal_lpdf(yn, mu, sg)
+    yz = y.copy()
+    yz[7] = 0.0
+    lp, g = glm.lognormal_lpdf(yz, mu, sg)
+    assert lp == -np.inf and g == {}
+    assert glm.lognormal_lpdf(yz, mu, sg, propto=True, var_mask=0)[0] == -np.inf
+    with pytest.raises(Exception):
+        glm.locscale_eval(3, y, mu, sg, glm.locscale_flags("cauchy"))
