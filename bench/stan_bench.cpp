@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|d3|d4|l1|l2|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|d3|d4|l1|l2|l3|l4|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -369,8 +369,11 @@ double locscale_once(const VectorXd& y, const VectorXd& mu_val, double sigma_val
   for (int64_t i = 0; i < mu_val.size(); ++i) mu[i] = mu_val[i];
   var sigma = sigma_val;
   const double t0 = now();
-  var lp = DENSITY == 1 ? (GPU ? cauchy_lpdf(y, mu, sigma) : cauchy_lpdf_reference_cpu<false>(y, mu, sigma))
-                        : (GPU ? lognormal_lpdf(y, mu, sigma) : lognormal_lpdf_reference_cpu<false>(y, mu, sigma));
+  // (3: gamma_lpdf(y | alpha = the scalar, beta = the vector), 4: exponential_lpdf(y | beta = the vector))
+  var lp = DENSITY == 1   ? (GPU ? cauchy_lpdf(y, mu, sigma) : cauchy_lpdf_reference_cpu<false>(y, mu, sigma))
+           : DENSITY == 2 ? (GPU ? lognormal_lpdf(y, mu, sigma) : lognormal_lpdf_reference_cpu<false>(y, mu, sigma))
+           : DENSITY == 3 ? (GPU ? gamma_lpdf(y, sigma, mu) : gamma_lpdf_reference_cpu<false>(y, sigma, mu))
+                          : (GPU ? exponential_lpdf(y, mu) + 0.0 * sigma : exponential_lpdf_reference_cpu<false>(y, mu) + 0.0 * sigma);
   grad(lp.vi_);
   out->lp = lp.val();
   out->grad.resize(mu.size() + 1);
@@ -588,21 +591,33 @@ int run(int argc, char** argv) {
     return 0;
   }
 
-  if (config == "l1" || config == "l2") {  // cauchy_lpdf, lognormal_lpdf
-    const bool cauchy = config == "l1";
+  if (config == "l1" || config == "l2" || config == "l3" || config == "l4") {  // cauchy, lognormal, gamma, exponential
+    const int which = config[1] - '0';
+    const bool cauchy = which == 1;
     const int64_t n = n_override ? n_override : 1000000;
     VectorXd y(n), mu(n);
-    Rng r(cauchy ? 1041 : 1042);
+    Rng r(1040 + which);
     for (int64_t i = 0; i < n; ++i) {
       y[i] = cauchy ? 2.0 * r.normal() : std::exp(1.2 * r.normal());
-      mu[i] = 0.1 * r.normal();
+      mu[i] = which >= 3 ? std::exp(0.3 * r.normal()) : 0.1 * r.normal();   // gamma / exponential: positive rates
     }
     Result g, c;
-    auto gpu = [&] { return cauchy ? locscale_once<true, 1>(y, mu, 1.3, &g) : locscale_once<true, 2>(y, mu, 1.3, &g); };
-    auto cpu = [&] { return cauchy ? locscale_once<false, 1>(y, mu, 1.3, &c) : locscale_once<false, 2>(y, mu, 1.3, &c); };
+    auto gpu = [&] {
+      return which == 1 ? locscale_once<true, 1>(y, mu, 1.3, &g) : which == 2 ? locscale_once<true, 2>(y, mu, 1.3, &g)
+             : which == 3 ? locscale_once<true, 3>(y, mu, 1.3, &g) : locscale_once<true, 4>(y, mu, 1.3, &g);
+    };
+    auto cpu = [&] {
+      return which == 1 ? locscale_once<false, 1>(y, mu, 1.3, &c) : which == 2 ? locscale_once<false, 2>(y, mu, 1.3, &c)
+             : which == 3 ? locscale_once<false, 3>(y, mu, 1.3, &c) : locscale_once<false, 4>(y, mu, 1.3, &c);
+    };
     gpu();
     Timing tg = time_reps(3, reps, 30, gpu);
-    std::printf("\"what\": \"%s N=%lld, y data, mu var vector, sigma var\", ", cauchy ? "cauchy_lpdf" : "lognormal_lpdf", (long long)n);
+    static const char* names[5] = {"", "cauchy_lpdf N=%lld, y data, mu var vector, sigma var", "lognormal_lpdf N=%lld, y data, mu var vector, sigma var",
+                                   "gamma_lpdf N=%lld, y data, alpha var, beta var vector", "exponential_lpdf N=%lld, y data, beta var vector"};
+    std::printf("\"what\": \"");
+    std::printf(names[which], (long long)n);
+    std::printf("\", ");
+    if (false) std::printf("%s N=%lld", cauchy ? "cauchy_lpdf" : "lognormal_lpdf", (long long)n);
     print_timing("gpu", tg);
     if (!no_cpu) {
       Timing tc = time_reps(1, std::max(cpu_reps, 5), 30, cpu);

@@ -187,6 +187,13 @@ typedef struct stan_cuda_normal_args {
 #define STAN_CUDA_LOCSCALE_NORMAL 0    /* normal_lpdf(y | mu, sigma)     prim/scal/prob/normal_lpdf.hpp:38-113 */
 #define STAN_CUDA_LOCSCALE_CAUCHY 1    /* cauchy_lpdf(y | mu, sigma)     prim/scal/prob/cauchy_lpdf.hpp:35-113 */
 #define STAN_CUDA_LOCSCALE_LOGNORMAL 2 /* lognormal_lpdf(y | mu, sigma)  prim/scal/prob/lognormal_lpdf.hpp:19-133 */
+/* two more densities of a real outcome on the same argument block (the names of its fields are normal_lpdf's):
+ *   gamma_lpdf(y | alpha, beta): alpha travels in mu / dmu, beta in sigma / dsigma.  Summands (gamma_lpdf.hpp:118-129):
+ *     LP_DOF = -lgamma(alpha), LP_SCALE = alpha * log(beta), LP_Y = (alpha - 1) * log(y), LP_MAIN = -beta * y.
+ *   exponential_lpdf(y | beta): beta in sigma / dsigma, mu is ignored (pass one zero).  Summands
+ *     (exponential_lpdf.hpp:76-81): LP_SCALE = log(beta), LP_MAIN = -beta * y. */
+#define STAN_CUDA_LOCSCALE_GAMMA 3       /* prim/scal/prob/gamma_lpdf.hpp:41-145 */
+#define STAN_CUDA_LOCSCALE_EXPONENTIAL 4 /* prim/scal/prob/exponential_lpdf.hpp:42-95 */
 /* lognormal only: the -sum log(y) term, which the reference ties to include_summand<propto, T_y>
  * (lognormal_lpdf.hpp:113-115) */
 #define STAN_CUDA_LP_Y 0x1000u
@@ -324,7 +331,9 @@ STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
  * LP_CONST = the constant (N * NEG_LOG_SQRT_TWO_PI | N * NEG_LOG_PI), LP_SCALE = -sum log(sigma), LP_MAIN = the
  * term every operand enters, LP_Y (lognormal) = -sum log(y).  Returns STAN_CUDA_BAD_OPERAND where the reference's
  * eager checks throw (cauchy_lpdf.hpp:47-49: y NaN, mu not finite, sigma not positive and finite; lognormal_lpdf.hpp:24-27:
- * also y negative) and STAN_CUDA_LOG_ZERO for lognormal_lpdf with an outcome equal to zero (:41-45). */
+ * also y negative; gamma_lpdf.hpp:55-57: y NaN, alpha or beta not positive and finite; exponential_lpdf.hpp:55-56: y NaN or
+ * negative, beta not positive and finite) and STAN_CUDA_LOG_ZERO for lognormal_lpdf with an outcome equal to zero (:41-45)
+ * and gamma_lpdf with a negative outcome (gamma_lpdf.hpp:69-74). */
 STAN_CUDA_API int stan_cuda_locscale_lpdf_eval(int32_t density, const stan_cuda_normal_args* a);
 /* Returns STAN_CUDA_BAD_OPERAND when an outcome is outside the density's support (bernoulli_logit: not in
  * {0, 1}, bernoulli_logit_lpmf.hpp:42; poisson_log: negative, poisson_log_lpmf.hpp:38) or the operand is NaN

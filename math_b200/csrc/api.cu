@@ -876,7 +876,7 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) { return locscale_lpdf_eval
 int locscale_lpdf_eval(int family, const stan_cuda_normal_args* a) {
   NvtxRange range("stan_cuda_locscale_lpdf_eval");
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: null args");
-  if (family < STAN_CUDA_LOCSCALE_NORMAL || family > STAN_CUDA_LOCSCALE_LOGNORMAL)
+  if (family < STAN_CUDA_LOCSCALE_NORMAL || family > STAN_CUDA_LOCSCALE_EXPONENTIAL)
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_locscale_lpdf_eval: unknown density");
   if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: negative n");
   if (a->n == 0) {  // size_zero(y, mu, sigma) -> 0 (normal_lpdf.hpp:45-47)
@@ -946,12 +946,13 @@ int locscale_lpdf_eval(int family, const stan_cuda_normal_args* a) {
   const double* res = td->h_pinned;
   if (a->lp) *a->lp = res[0];
   if (need_mu && !mv) a->dmu[0] = res[1];
-  if (need_y && !yv) a->dy[0] = family == STAN_CUDA_LOCSCALE_LOGNORMAL ? res[5] : -res[1];
+  if (need_y && !yv) a->dy[0] = family >= STAN_CUDA_LOCSCALE_LOGNORMAL ? res[5] : -res[1];
   if (need_sigma && !sv) a->dsigma[0] = res[2];
   counters().evals.fetch_add(1, std::memory_order_relaxed);
   const unsigned bits = unsigned(res[4]);
   if (bits & 7u) return STAN_CUDA_BAD_OPERAND;
-  if (bits & 8u) {  // lognormal_lpdf with an outcome equal to zero: LOG_ZERO, no partials (lognormal_lpdf.hpp:41-45)
+  if (bits & 8u) {  // lognormal_lpdf with an outcome equal to zero (lognormal_lpdf.hpp:41-45), gamma_lpdf with a negative one
+                    // (gamma_lpdf.hpp:69-74): LOG_ZERO, no partials
     if (a->lp) *a->lp = -INFINITY;
     return STAN_CUDA_LOG_ZERO;
   }

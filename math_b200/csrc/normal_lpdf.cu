@@ -5,7 +5,7 @@
 // through broadcast_array, prim/scal/meta/broadcast_array.hpp:9-33).
 #include <math.h>
 
-#include "common.cuh"
+#include "glm_device.cuh"  // digamma_pos
 
 namespace stancuda {
 
@@ -19,6 +19,8 @@ struct NormalKernelParams {
 // different per-element term:
 //   cauchy_lpdf     stan/math/prim/scal/prob/cauchy_lpdf.hpp:60-108
 //   lognormal_lpdf  stan/math/prim/scal/prob/lognormal_lpdf.hpp:41-131
+//   gamma_lpdf      stan/math/prim/scal/prob/gamma_lpdf.hpp:69-145        (alpha in the mu slot, beta in the sigma slot)
+//   exponential_lpdf stan/math/prim/scal/prob/exponential_lpdf.hpp:55-90  (beta in the sigma slot, mu unused)
 template <int FAMILY, int THREADS>
 __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernelParams p) {
   const NormalIO& io = p.io;
@@ -42,7 +44,9 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
       inv_sigma = 1.0 / sg;
       if (lp_scale) log_sigma = log(sg);
     }
-    bad |= (isnan(y) ? 1u : 0u) | (isfinite(mu) ? 0u : 2u);
+    bad |= isnan(y) ? 1u : 0u;
+    if (FAMILY == STAN_CUDA_LOCSCALE_GAMMA) bad |= (mu > 0.0 && isfinite(mu)) ? 0u : 2u;  // the shape: positive and finite
+    else if (FAMILY != STAN_CUDA_LOCSCALE_EXPONENTIAL) bad |= isfinite(mu) ? 0u : 2u;
     if (io.sigma_vec) bad |= (sg > 0.0 && (FAMILY == STAN_CUDA_LOCSCALE_NORMAL || isfinite(sg))) ? 0u : 4u;
     double lp = 0.0, d_mu, d_sigma, d_y;
     if (FAMILY == STAN_CUDA_LOCSCALE_NORMAL) {
@@ -65,6 +69,25 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
       d_mu = 2.0 * y_minus_mu / (sigma_squared + y_minus_mu_squared);                                   // :101-104
       d_y = -d_mu;                                                                                      // :97-100
       d_sigma = (y_minus_mu_squared - sigma_squared) * inv_sigma / (sigma_squared + y_minus_mu_squared);  // :105-109
+    } else if (FAMILY == STAN_CUDA_LOCSCALE_GAMMA) {
+      // gamma_lpdf.hpp:69-145 with alpha = mu, beta = sg; the four summands have a flag each (include/stan_cuda.h)
+      bad |= (y < 0.0) ? 8u : 0u;                      // :69-74 LOG_ZERO
+      const double log_y = y > 0.0 ? log(y) : 0.0;     // :86-90 (an outcome of zero leaves the builder's zero)
+      const double log_beta = log(sg);                 // :109-113
+      if (io.flags & STAN_CUDA_LP_DOF) lp -= lgamma(mu);               // :118-120
+      if (lp_scale) lp += mu * log_beta;                                 // :121-123
+      if (lp_y) lp += (mu - 1.0) * log_y;                                // :124-126
+      if (lp_main) lp -= sg * y;                                         // :127-129
+      d_y = (mu - 1.0) / y - sg;                                         // :131-133
+      d_mu = (io.flags & STAN_CUDA_NEED_DALPHA) ? -digamma_pos(mu) + log_beta + log_y : 0.0;  // :134-137
+      d_sigma = mu / sg - y;                                             // :138-140
+    } else if (FAMILY == STAN_CUDA_LOCSCALE_EXPONENTIAL) {
+      bad |= (y < 0.0) ? 1u : 0u;                      // exponential_lpdf.hpp:55 check_nonnegative(y)
+      if (lp_scale) lp += log(sg);                     // :76-78
+      if (lp_main) lp -= sg * y;                       // :79-81
+      d_y = -sg;                                       // :83-85
+      d_mu = 0.0;
+      d_sigma = 1.0 / sg - y;                          // :86-88
     } else {
       bad |= (y < 0.0) ? 1u : 0u;                      // :25 check_nonnegative(y)
       bad |= (y == 0.0) ? 8u : 0u;                     // :41-45
@@ -160,6 +183,12 @@ int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream
       break;
     case STAN_CUDA_LOCSCALE_LOGNORMAL:
       normal_lpdf_kernel<STAN_CUDA_LOCSCALE_LOGNORMAL, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_LOCSCALE_GAMMA:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_GAMMA, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_LOCSCALE_EXPONENTIAL:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_EXPONENTIAL, THREADS><<<grid, THREADS, 0, stream>>>(p);
       break;
     default:
       return fail(STAN_CUDA_ERR_ARG, "launch_normal_lpdf: unknown density");

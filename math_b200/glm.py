@@ -494,15 +494,23 @@ def locscale_flags(density, propto=False, var_mask=0b110):
     """Which summands the reference keeps under include_summand<propto, ...> (normal_lpdf.hpp:89-97,
     cauchy_lpdf.hpp:87-95, lognormal_lpdf.hpp:92-118) for the operands that are variables (var_mask bit 0: y, 1: mu,
     2: sigma), and which partials they need."""
+    d = _abi.LOCSCALES[density] if isinstance(density, str) else density
     vy, vm, vs = bool(var_mask & 1), bool(var_mask & 2), bool(var_mask & 4)
     f = (_abi.NEED_DY if vy else 0) | (_abi.NEED_DALPHA if vm else 0) | (_abi.NEED_DSIGMA if vs else 0)
+    if d == _abi.LOCSCALE_GAMMA:        # gamma_lpdf.hpp:118-129 (alpha = the mu operand, beta = the sigma operand)
+        f |= (_abi.LP_DOF if (not propto or vm) else 0) | (_abi.LP_SCALE if (not propto or vm or vs) else 0)
+        f |= (_abi.LP_Y if (not propto or vy or vm) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
+        return f
+    if d == _abi.LOCSCALE_EXPONENTIAL:  # exponential_lpdf.hpp:76-81 (beta = the sigma operand)
+        f &= ~_abi.NEED_DALPHA
+        return f | (_abi.LP_SCALE if (not propto or vs) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
     if not propto:
         f |= _abi.LP_CONST
     if not propto or vs:
         f |= _abi.LP_SCALE
     if not propto or vy or vm or vs:
         f |= _abi.LP_MAIN
-    if density in ("lognormal", _abi.LOCSCALE_LOGNORMAL) and (not propto or vy):
+    if d == _abi.LOCSCALE_LOGNORMAL and (not propto or vy):
         f |= _abi.LP_Y
     return f
 
@@ -516,6 +524,58 @@ def cauchy_lpdf(y, mu, sigma, propto=False, var_mask=0b110, y_is_data=True):
 def lognormal_lpdf(y, mu, sigma, propto=False, var_mask=0b110, y_is_data=True):
     """stan/math/prim/scal/prob/lognormal_lpdf.hpp:19-21; var_mask and grads as for cauchy_lpdf."""
     return _locscale_lpdf("lognormal_lpdf", "lognormal", y, mu, sigma, propto, var_mask, y_is_data)
+
+def gamma_lpdf(y, alpha, beta, propto=False, var_mask=0b110, y_is_data=True):
+    """stan/math/prim/scal/prob/gamma_lpdf.hpp:41-43; var_mask: which of y (bit 0), alpha (1), beta (2) are variables;
+    grads: the partials of those.  Call sequence :48-74: size_zero, domain errors, size error, nothing to compute -> 0,
+    a negative outcome -> LOG_ZERO."""
+    f = "gamma_lpdf"
+    y, alpha, beta = _f64(y), _f64(alpha), _f64(beta)
+    if min(y.size, alpha.size, beta.size) == 0:
+        return 0.0, {}
+    if np.any(np.isnan(y)):
+        raise DomainError("%s: Random variable is nan" % f)
+    if not np.all((alpha > 0) & np.isfinite(alpha)):
+        raise DomainError("%s: Shape parameter must be positive finite" % f)
+    if not np.all((beta > 0) & np.isfinite(beta)):
+        raise DomainError("%s: Inverse scale parameter must be positive finite" % f)
+    n = max(y.size, alpha.size, beta.size)
+    for name, v in (("Random variable", y), ("Shape parameter", alpha), ("Inverse scale parameter", beta)):
+        if v.size != 1 and v.size != n:
+            raise ValueError("%s: %s has dimension = %d, expecting dimension = %d" % (f, name, v.size, n))
+    if propto and var_mask == 0:
+        return 0.0, {}
+    r = locscale_eval("gamma", y, alpha, beta, locscale_flags("gamma", propto, var_mask), y_is_data=y_is_data and not (var_mask & 1))
+    if r["rc"] == _abi.BAD_OPERAND:
+        raise DomainError("%s: operand outside the domain" % f)
+    if r["rc"] == _abi.LOG_ZERO:
+        return -np.inf, {}
+    return r["lp"], {name: r[key] for name, key, bit in (("y", "dy", 1), ("alpha", "dmu", 2), ("beta", "dsigma", 4)) if var_mask & bit}
+
+
+def exponential_lpdf(y, beta, propto=False, var_mask=0b10, y_is_data=True):
+    """stan/math/prim/scal/prob/exponential_lpdf.hpp:42-44; var_mask: which of y (bit 0), beta (bit 1) are variables."""
+    f = "exponential_lpdf"
+    y, beta = _f64(y), _f64(beta)
+    if min(y.size, beta.size) == 0:
+        return 0.0, {}
+    if not np.all(y >= 0):
+        raise DomainError("%s: Random variable must be >= 0" % f)
+    if not np.all((beta > 0) & np.isfinite(beta)):
+        raise DomainError("%s: Inverse scale parameter must be positive finite" % f)
+    n = max(y.size, beta.size)
+    for name, v in (("Random variable", y), ("Inverse scale parameter", beta)):
+        if v.size != 1 and v.size != n:
+            raise ValueError("%s: %s has dimension = %d, expecting dimension = %d" % (f, name, v.size, n))
+    mask3 = (var_mask & 1) | ((var_mask & 2) << 1)   # y -> bit 0, beta -> the sigma operand's bit 2
+    if propto and var_mask == 0:
+        return 0.0, {}
+    r = locscale_eval("exponential", y, [0.0], beta, locscale_flags("exponential", propto, mask3),
+                      y_is_data=y_is_data and not (var_mask & 1))
+    if r["rc"] == _abi.BAD_OPERAND:
+        raise DomainError("%s: operand outside the domain" % f)
+    return r["lp"], {name: r[key] for name, key, bit in (("y", "dy", 1), ("beta", "dsigma", 4)) if mask3 & bit}
+
 
 def student_t_eval(y, nu, mu, sigma, flags, y_is_data=True):
     """One stan_cuda_student_t_lpdf_eval call; returns {"rc", "lp", "dy", "dnu", "dmu", "dsigma"} (partials for the

@@ -366,12 +366,62 @@ int oracle_normal_lpdf_eval(const stan_cuda_normal_args* a) {
  * itself with its eager checks (normal_lpdf.hpp:51-53) turned into BAD_OPERAND.  Scalar operands accumulate their
  * partial over n (broadcast_array). */
 #define ORACLE_NEG_LOG_PI (-1.14472988584940017414342735135)
+/* gamma_lpdf(y | alpha, beta) (stan/math/prim/scal/prob/gamma_lpdf.hpp:41-145; alpha in the mu slot, beta in the sigma
+ * slot) and exponential_lpdf(y | beta) (exponential_lpdf.hpp:42-95; beta in the sigma slot, mu ignored) */
+static int oracle_gamma_exponential(int density, const stan_cuda_normal_args* a) {
+  const int gam = density == STAN_CUDA_LOCSCALE_GAMMA;
+  for (int64_t i = 0; i < a->y_len; ++i)
+    if (isnan(a->y[i]) || (!gam && a->y[i] < 0)) return STAN_CUDA_BAD_OPERAND;              /* gamma :55, exponential :55 */
+  if (gam)
+    for (int64_t i = 0; i < a->mu_len; ++i)
+      if (!(a->mu[i] > 0.0) || !isfinite(a->mu[i])) return STAN_CUDA_BAD_OPERAND;           /* :56 */
+  for (int64_t i = 0; i < a->sigma_len; ++i)
+    if (!(a->sigma[i] > 0.0) || !isfinite(a->sigma[i])) return STAN_CUDA_BAD_OPERAND;       /* :57 / :56 */
+  if (gam)
+    for (int64_t i = 0; i < a->y_len; ++i)
+      if (a->y[i] < 0) {                                                                    /* :69-74 */
+        if (a->lp) *a->lp = -INFINITY;
+        return STAN_CUDA_LOG_ZERO;
+      }
+  const int ym = a->y_len != 1, mm = a->mu_len != 1, sm = a->sigma_len != 1;
+  const int need_mu = gam && (a->flags & STAN_CUDA_NEED_DALPHA) && a->dmu;
+  const int need_sigma = (a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma;
+  const int need_y = (a->flags & STAN_CUDA_NEED_DY) && a->dy;
+  if (need_mu) for (int64_t i = 0; i < a->mu_len; ++i) a->dmu[i] = 0.0;
+  if (need_sigma) for (int64_t i = 0; i < a->sigma_len; ++i) a->dsigma[i] = 0.0;
+  if (need_y) for (int64_t i = 0; i < a->y_len; ++i) a->dy[i] = 0.0;
+  double logp = 0.0;
+  for (int64_t n = 0; n < a->n; ++n) {
+    const double y = a->y[ym ? n : 0], beta = a->sigma[sm ? n : 0];
+    if (gam) {
+      const double alpha = a->mu[mm ? n : 0];
+      const double log_y = y > 0 ? log(y) : 0.0;                                            /* :86-90 */
+      const double log_beta = log(beta);
+      if (a->flags & STAN_CUDA_LP_DOF) logp -= lgamma(alpha);                               /* :118-120 */
+      if (a->flags & STAN_CUDA_LP_SCALE) logp += alpha * log_beta;                          /* :121-123 */
+      if (a->flags & STAN_CUDA_LP_Y) logp += (alpha - 1.0) * log_y;                         /* :124-126 */
+      if (a->flags & STAN_CUDA_LP_MAIN) logp -= beta * y;                                   /* :127-129 */
+      if (need_y) a->dy[ym ? n : 0] += (alpha - 1) / y - beta;                              /* :131-133 */
+      if (need_mu) a->dmu[mm ? n : 0] += -oracle_digamma(alpha) + log_beta + log_y;         /* :134-137 */
+      if (need_sigma) a->dsigma[sm ? n : 0] += alpha / beta - y;                            /* :138-140 */
+    } else {
+      if (a->flags & STAN_CUDA_LP_SCALE) logp += log(beta);                                 /* :76-78 */
+      if (a->flags & STAN_CUDA_LP_MAIN) logp -= beta * y;                                   /* :79-81 */
+      if (need_y) a->dy[ym ? n : 0] -= beta;                                                /* :83-85 */
+      if (need_sigma) a->dsigma[sm ? n : 0] += 1 / beta - y;                                /* :86-88 */
+    }
+  }
+  if (a->lp) *a->lp = logp;
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
 int oracle_locscale_lpdf_eval(int density, const stan_cuda_normal_args* a) {
-  if (!a || a->n < 0 || density < STAN_CUDA_LOCSCALE_NORMAL || density > STAN_CUDA_LOCSCALE_LOGNORMAL) return STAN_CUDA_ERR_ARG;
+  if (!a || a->n < 0 || density < STAN_CUDA_LOCSCALE_NORMAL || density > STAN_CUDA_LOCSCALE_EXPONENTIAL) return STAN_CUDA_ERR_ARG;
   if (a->n == 0) {
     if (a->lp) *a->lp = 0.0;
     return STAN_CUDA_OK;
   }
+  if (density >= STAN_CUDA_LOCSCALE_GAMMA) return oracle_gamma_exponential(density, a);
   const int lognormal = density == STAN_CUDA_LOCSCALE_LOGNORMAL, normal = density == STAN_CUDA_LOCSCALE_NORMAL;
   for (int64_t i = 0; i < a->y_len; ++i)
     if (isnan(a->y[i]) || (lognormal && a->y[i] < 0)) return STAN_CUDA_BAD_OPERAND;          /* cauchy :47, lognormal :24-25 */

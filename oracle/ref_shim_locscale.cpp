@@ -1,7 +1,8 @@
 // oracle/ref_shim_locscale.cpp -- TEST INFRASTRUCTURE, a translation unit of _ref/libstanref.so.
 //
-// The UNMODIFIED reference's normal_lpdf / cauchy_lpdf / lognormal_lpdf (stan/math/prim/scal/prob/normal_lpdf.hpp:38-113,
-// cauchy_lpdf.hpp:35-113, lognormal_lpdf.hpp:19-133) behind one C entry point, for every mix of {double, var} x
+// The UNMODIFIED reference's normal_lpdf / cauchy_lpdf / lognormal_lpdf / gamma_lpdf / exponential_lpdf
+// (stan/math/prim/scal/prob/normal_lpdf.hpp:38-113, cauchy_lpdf.hpp:35-113, lognormal_lpdf.hpp:19-133, gamma_lpdf.hpp:41-145,
+// exponential_lpdf.hpp:42-95) behind one C entry point, for every mix of {double, var} x
 // {scalar, vector} over the three operands, so that the parity tests can check each `propto` summand selection and
 // each partial against the reference itself.  Compiled from the headers where they lie under /root/reference
 // (oracle/Makefile); nothing is copied.
@@ -78,6 +79,21 @@ struct Call<2, propto> {
   }
 };
 
+template <bool propto>
+struct Call<3, propto> {  // gamma_lpdf(y | alpha, beta): alpha in the mu slot, beta in the sigma slot
+  template <typename A, typename B, typename C>
+  static auto go(const A& y, const B& alpha, const C& beta) -> decltype(stan::math::gamma_lpdf<propto>(y, alpha, beta)) {
+    return stan::math::gamma_lpdf<propto>(y, alpha, beta);
+  }
+};
+template <bool propto>
+struct Call<4, propto> {  // exponential_lpdf(y | beta): beta in the sigma slot, the mu slot is ignored
+  template <typename A, typename B, typename C>
+  static auto go(const A& y, const B&, const C& beta) -> decltype(stan::math::exponential_lpdf<propto>(y, beta)) {
+    return stan::math::exponential_lpdf<propto>(y, beta);
+  }
+};
+
 // peel one operand at a time into its static type, then call the reference
 template <int FAMILY, bool propto, typename... Done>
 struct Dispatch {
@@ -106,7 +122,8 @@ double run_family(bool propto, const Operand& y, const Operand& mu, const Operan
 
 extern "C" {
 
-// density 0: normal_lpdf, 1: cauchy_lpdf, 2: lognormal_lpdf.  var_mask bit 0: y, bit 1: mu, bit 2: sigma.  Lengths are 1
+// density 0: normal_lpdf, 1: cauchy_lpdf, 2: lognormal_lpdf, 3: gamma_lpdf(y | alpha = mu, beta = sigma),
+// 4: exponential_lpdf(y | beta = sigma; pass mu as one double).  var_mask bit 0: y, bit 1: mu, bit 2: sigma.  Lengths are 1
 // (scalar) or n (vector).  Returns 0, or 1 (std::domain_error) / 2 (std::invalid_argument) / 3 (other) with the
 // exception text in err.
 int stanref_locscale_lpdf(int density, int propto, int var_mask, const double* y, long y_len, const double* mu, long mu_len,
@@ -117,8 +134,10 @@ int stanref_locscale_lpdf(int density, int propto, int var_mask, const double* y
     Operand oy{y, y_len, var_mask & 1}, om{mu, mu_len, (var_mask >> 1) & 1}, os{sigma, sigma_len, (var_mask >> 2) & 1};
     oy.build(); om.build(); os.build();
     auto t0 = std::chrono::steady_clock::now();
-    const double r = density == 0 ? run_family<0>(propto != 0, oy, om, os)
-                     : density == 1 ? run_family<1>(propto != 0, oy, om, os) : run_family<2>(propto != 0, oy, om, os);
+    const double r = density == 0   ? run_family<0>(propto != 0, oy, om, os)
+                     : density == 1 ? run_family<1>(propto != 0, oy, om, os)
+                     : density == 2 ? run_family<2>(propto != 0, oy, om, os)
+                     : density == 3 ? run_family<3>(propto != 0, oy, om, os) : run_family<4>(propto != 0, oy, om, os);
     auto t1 = std::chrono::steady_clock::now();
     if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
     if (lp) *lp = r;

@@ -14,7 +14,7 @@ namespace math {
 namespace cuda {
 
 /**
- * cauchy_lpdf and lognormal_lpdf on the device: the operands, their staging and the tape node are
+ * cauchy_lpdf, lognormal_lpdf, gamma_lpdf and exponential_lpdf on the device: the operands, their staging and the tape node are
  * those of normal_lpdf_device (stan/math/cuda/normal_lpdf.hpp); the density id selects the per-element term of the
  * kernel (stan_cuda_locscale_lpdf_eval).  Eligible calls: the vectorised ones with something to compute -- when
  * include_summand<propto, T_y, T_loc, T_scale> is false the reference body only runs its checks, and stays in charge.
@@ -35,6 +35,10 @@ struct cauchy_checks {
     check_finite(function(), "Location parameter", mu);
     check_positive_finite(function(), "Scale parameter", sigma);
   }
+  template <typename T_y, typename T_loc, typename T_scale>
+  static void sizes(const T_y& y, const T_loc& mu, const T_scale& sigma) {
+    check_consistent_sizes(function(), "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
+  }
 };
 /** the eager checks of lognormal_lpdf.hpp:24-27 */
 struct lognormal_checks {
@@ -46,14 +50,46 @@ struct lognormal_checks {
     check_finite(function(), "Location parameter", mu);
     check_positive_finite(function(), "Scale parameter", sigma);
   }
+  template <typename T_y, typename T_loc, typename T_scale>
+  static void sizes(const T_y& y, const T_loc& mu, const T_scale& sigma) {
+    check_consistent_sizes(function(), "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
+  }
+};
+
+/** the eager checks of gamma_lpdf.hpp:55-57 (alpha in the location slot, beta in the scale slot) */
+struct gamma_checks {
+  static const char* function() { return "gamma_lpdf"; }
+  template <typename T_y, typename T_shape, typename T_inv_scale>
+  static void run(const T_y& y, const T_shape& alpha, const T_inv_scale& beta) {
+    check_not_nan(function(), "Random variable", y);
+    check_positive_finite(function(), "Shape parameter", alpha);
+    check_positive_finite(function(), "Inverse scale parameter", beta);
+  }
+  template <typename T_y, typename T_shape, typename T_inv_scale>
+  static void sizes(const T_y& y, const T_shape& alpha, const T_inv_scale& beta) {
+    check_consistent_sizes(function(), "Random variable", y, "Shape parameter", alpha, "Inverse scale parameter", beta);
+  }
+};
+/** the eager checks of exponential_lpdf.hpp:55-56 (beta in the scale slot; the location slot holds one zero) */
+struct exponential_checks {
+  static const char* function() { return "exponential_lpdf"; }
+  template <typename T_y, typename T_unused, typename T_inv_scale>
+  static void run(const T_y& y, const T_unused&, const T_inv_scale& beta) {
+    check_nonnegative(function(), "Random variable", y);
+    check_positive_finite(function(), "Inverse scale parameter", beta);
+  }
+  template <typename T_y, typename T_unused, typename T_inv_scale>
+  static void sizes(const T_y& y, const T_unused&, const T_inv_scale& beta) {
+    check_consistent_sizes(function(), "Random variable", y, "Inverse scale parameter", beta);
+  }
 };
 
 /**
  * One vectorised evaluation: stages the operands, builds the tape node in place (arena_partials), calls the device.
- * extra_flags: summand bits beyond the ones every location-scale density shares (lognormal: STAN_CUDA_LP_Y).
+ * summands: the STAN_CUDA_LP_* bits of the terms the reference keeps for these operand types under this propto.
  */
-template <bool propto, typename Checks, typename T_y, typename T_loc, typename T_scale>
-return_type_t<T_y, T_loc, T_scale> locscale_lpdf_call(int density, uint32_t extra_flags, const T_y& y, const T_loc& mu,
+template <typename Checks, typename T_y, typename T_loc, typename T_scale>
+return_type_t<T_y, T_loc, T_scale> locscale_lpdf_call(int density, uint32_t summands, const T_y& y, const T_loc& mu,
                                                       const T_scale& sigma) {
   const char* function = Checks::function();
   // the reference reports a domain error before a size error: if the sizes disagree, its checks run in its order
@@ -61,7 +97,7 @@ return_type_t<T_y, T_loc, T_scale> locscale_lpdf_call(int density, uint32_t extr
   if ((is_vector<T_y>::value && length(y) != N) || (is_vector<T_loc>::value && length(mu) != N)
       || (is_vector<T_scale>::value && length(sigma) != N)) {
     Checks::run(y, mu, sigma);
-    check_consistent_sizes(function, "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
+    Checks::sizes(y, mu, sigma);
   }
   const size_t by = staged_operand<T_y>::bytes(y), bm = staged_operand<T_loc>::bytes(mu),
                bs = staged_operand<T_scale>::bytes(sigma);
@@ -89,13 +125,7 @@ return_type_t<T_y, T_loc, T_scale> locscale_lpdf_call(int density, uint32_t extr
   a.sigma = gathered_by_node<T_scale>::value ? stage_sigma : staged_operand<T_scale>::fill(sigma, stage_sigma);
   a.sigma_len = length(sigma);
   a.lp = &logp;
-  a.flags = STAN_CUDA_LP_MAIN | extra_flags;
-  if (include_summand<propto>::value) {
-    a.flags |= STAN_CUDA_LP_CONST;
-  }
-  if (include_summand<propto, T_scale>::value) {
-    a.flags |= STAN_CUDA_LP_SCALE;
-  }
+  a.flags = summands;
   if (!is_constant_all<T_y>::value) {
     a.flags |= STAN_CUDA_NEED_DY;
     a.dy = ops_partials.partials(0);
@@ -132,7 +162,9 @@ return_type_t<T_y, T_loc, T_scale> cauchy_lpdf_device(const T_y& y, const T_loc&
   if (size_zero(y, mu, sigma)) {
     return 0.0;
   }
-  return detail::locscale_lpdf_call<propto, detail::cauchy_checks>(STAN_CUDA_LOCSCALE_CAUCHY, 0u, y, mu, sigma);
+  const uint32_t summands = STAN_CUDA_LP_MAIN | (include_summand<propto>::value ? STAN_CUDA_LP_CONST : 0u)   // :87-95
+                            | (include_summand<propto, T_scale>::value ? STAN_CUDA_LP_SCALE : 0u);
+  return detail::locscale_lpdf_call<detail::cauchy_checks>(STAN_CUDA_LOCSCALE_CAUCHY, summands, y, mu, sigma);
 }
 
 /**
@@ -145,11 +177,47 @@ template <bool propto, typename T_y, typename T_loc, typename T_scale>
 return_type_t<T_y, T_loc, T_scale> lognormal_lpdf_device(const T_y& y, const T_loc& mu, const T_scale& sigma) {
   if (size_zero(y, mu, sigma)) {
     detail::lognormal_checks::run(y, mu, sigma);
-    check_consistent_sizes("lognormal_lpdf", "Random variable", y, "Location parameter", mu, "Scale parameter", sigma);
+    detail::lognormal_checks::sizes(y, mu, sigma);
     return 0.0;
   }
-  return detail::locscale_lpdf_call<propto, detail::lognormal_checks>(
-      STAN_CUDA_LOCSCALE_LOGNORMAL, include_summand<propto, T_y>::value ? STAN_CUDA_LP_Y : 0u, y, mu, sigma);
+  const uint32_t summands = STAN_CUDA_LP_MAIN | (include_summand<propto>::value ? STAN_CUDA_LP_CONST : 0u)   // :92-118
+                            | (include_summand<propto, T_scale>::value ? STAN_CUDA_LP_SCALE : 0u)
+                            | (include_summand<propto, T_y>::value ? STAN_CUDA_LP_Y : 0u);
+  return detail::locscale_lpdf_call<detail::lognormal_checks>(STAN_CUDA_LOCSCALE_LOGNORMAL, summands, y, mu, sigma);
+}
+
+/**
+ * GPU body of the vectorised gamma_lpdf (reference: stan/math/prim/scal/prob/gamma_lpdf.hpp:41-145): the loops :69-141
+ * become one kernel -- lgamma and digamma of the shape included --, with the reference's four summand conditions
+ * (:118-129) as four flags, its LOG_ZERO for a negative outcome (:69-74) and the zero it leaves in log_y for an outcome of
+ * zero (:86-90).
+ */
+template <bool propto, typename T_y, typename T_shape, typename T_inv_scale>
+return_type_t<T_y, T_shape, T_inv_scale> gamma_lpdf_device(const T_y& y, const T_shape& alpha, const T_inv_scale& beta) {
+  if (size_zero(y, alpha, beta)) {
+    return 0.0;
+  }
+  const uint32_t summands = (include_summand<propto, T_shape>::value ? STAN_CUDA_LP_DOF : 0u)
+                            | (include_summand<propto, T_shape, T_inv_scale>::value ? STAN_CUDA_LP_SCALE : 0u)
+                            | (include_summand<propto, T_y, T_shape>::value ? STAN_CUDA_LP_Y : 0u)
+                            | (include_summand<propto, T_y, T_inv_scale>::value ? STAN_CUDA_LP_MAIN : 0u);
+  return detail::locscale_lpdf_call<detail::gamma_checks>(STAN_CUDA_LOCSCALE_GAMMA, summands, y, alpha, beta);
+}
+
+/**
+ * GPU body of the vectorised exponential_lpdf (reference: stan/math/prim/scal/prob/exponential_lpdf.hpp:42-95).  The
+ * argument block's location slot carries one constant zero: a double operand adds no edge to the tape node, which
+ * therefore holds the same operands in the same order as the reference's operands_and_partials<T_y, T_inv_scale>.
+ */
+template <bool propto, typename T_y, typename T_inv_scale>
+return_type_t<T_y, T_inv_scale> exponential_lpdf_device(const T_y& y, const T_inv_scale& beta) {
+  if (size_zero(y, beta)) {
+    return 0.0;
+  }
+  const uint32_t summands = (include_summand<propto, T_inv_scale>::value ? STAN_CUDA_LP_SCALE : 0u)           // :76-81
+                            | (include_summand<propto, T_y, T_inv_scale>::value ? STAN_CUDA_LP_MAIN : 0u);
+  const double unused = 0.0;
+  return detail::locscale_lpdf_call<detail::exponential_checks>(STAN_CUDA_LOCSCALE_EXPONENTIAL, summands, y, unused, beta);
 }
 
 }  // namespace cuda

@@ -1,5 +1,6 @@
 // The reference's distribution-test fixture (test/prob/test_fixture_distr.hpp) and its cauchy and lognormal test
-// classes (test/prob/cauchy/cauchy_test.hpp, test/prob/lognormal/lognormal_test.hpp: known answers, invalid values),
+// classes and those of gamma and exponential (test/prob/{cauchy,lognormal,gamma,exponential}/*_test.hpp: known answers,
+// invalid values),
 // all included UNMODIFIED from the reference tree and instantiated -- the way the reference's generator
 // (test/prob/generate_tests.cpp:235-340) writes its "_v_" files -- for argument kinds the overlay routes to the
 // B200 kernel (at least one container operand of double / var) plus one all-scalar kind that stays on the
@@ -11,6 +12,8 @@
 #include <test/prob/test_fixture_distr.hpp>
 #include <test/prob/cauchy/cauchy_test.hpp>
 #include <test/prob/lognormal/lognormal_test.hpp>
+#include <test/prob/gamma/gamma_test.hpp>
+#include <test/prob/exponential/exponential_test.hpp>
 #include <vector>
 
 typedef Eigen::Matrix<var, Eigen::Dynamic, 1> vector_var;
@@ -47,4 +50,29 @@ STAN_CUDA_DISTR(AgradDistributionsLognormal, 4)
 STAN_CUDA_DISTR(AgradDistributionsLognormal, 5)
 STAN_CUDA_DISTR(AgradDistributionsLognormal, 6)
 STAN_CUDA_DISTR(AgradDistributionsLognormal, 7)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 0)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 1)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 2)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 3)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 4)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 5)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 6)
+STAN_CUDA_DISTR(AgradDistributionsGamma, 7)
+
+// exponential_lpdf(y | beta): two operands
+typedef boost::mpl::vector<std::vector<double>, var, empty, empty, empty, empty> type_e_0;   // data y, var rate: the model statement
+typedef boost::mpl::vector<vector_dbl, vector_var, empty, empty, empty, empty> type_e_1;
+typedef boost::mpl::vector<std::vector<var>, std::vector<var>, empty, empty, empty, empty> type_e_2;
+typedef boost::mpl::vector<vector_var, double, empty, empty, empty, empty> type_e_3;
+typedef boost::mpl::vector<double, row_vector_var, empty, empty, empty, empty> type_e_4;
+typedef boost::mpl::vector<var, var, empty, empty, empty, empty> type_e_5;  // all scalars: reference loop
+#define STAN_CUDA_DISTR_E(TEST_CLASS, N)                                                    \
+  typedef boost::mpl::vector<TEST_CLASS, type_e_##N> TEST_CLASS##_e_##N;                    \
+  INSTANTIATE_TYPED_TEST_CASE_P(TEST_CLASS##_e_##N, AgradDistributionTestFixture, TEST_CLASS##_e_##N);
+STAN_CUDA_DISTR_E(AgradDistributionsExponential, 0)
+STAN_CUDA_DISTR_E(AgradDistributionsExponential, 1)
+STAN_CUDA_DISTR_E(AgradDistributionsExponential, 2)
+STAN_CUDA_DISTR_E(AgradDistributionsExponential, 3)
+STAN_CUDA_DISTR_E(AgradDistributionsExponential, 4)
+STAN_CUDA_DISTR_E(AgradDistributionsExponential, 5)
 #endif

@@ -1,4 +1,4 @@
-// cauchy_lpdf / lognormal_lpdf on the device through the reference's own C++ signatures, against the
+// cauchy_lpdf / lognormal_lpdf / gamma_lpdf / exponential_lpdf on the device through the reference's own C++ signatures, against the
 // unmodified reference bodies (reachable in the same binary as *_reference_cpu, see overlay/), at the north star's
 // tolerance: every mix of var / double and vector / scalar operands that the overlay routes, propto on and off, the
 // reference's exceptions and its LOG_ZERO.
@@ -123,7 +123,111 @@ TEST_P(CudaLocScale, lognormal_matches_reference_loop) {
   stan::math::recover_memory();
 }
 
+TEST_P(CudaLocScale, gamma_and_exponential_match_reference_loop) {
+  const int n = GetParam();
+  Data d = make(n, 300 + n);
+  VectorXd al_d = d.sigma.array() + 0.2;  // shapes in (0.5, 3.2)
+  vector_v y = to_v(d.y_pos), alpha = to_v(al_d), beta = to_v(d.sigma);
+  var alpha0 = 2.2, beta0 = 1.3;
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("gamma, all var vectors", gamma_lpdf(y, alpha, beta), gamma_lpdf_reference_cpu<false>(y, alpha, beta), adj(y),
+                   adj(beta));
+  STAN_CUDA_PARITY("gamma, the model statement", gamma_lpdf(d.y_pos, alpha0, beta), gamma_lpdf_reference_cpu<false>(d.y_pos, alpha0, beta),
+                   adj(beta));
+  STAN_CUDA_PARITY("gamma propto, data y", gamma_lpdf<true>(d.y_pos, alpha0, beta), gamma_lpdf_reference_cpu<true>(d.y_pos, alpha0, beta),
+                   adj(beta));
+  STAN_CUDA_PARITY("gamma propto, var y only", gamma_lpdf<true>(y, al_d, d.sigma), gamma_lpdf_reference_cpu<true>(y, al_d, d.sigma),
+                   adj(y));
+  {  // d/dalpha = -digamma(alpha) + log(beta) + log(y): accurate to the magnitude of its terms (see tests/test_locscale.py)
+    var lp = gamma_lpdf(d.y_pos, alpha, beta0);
+    lp.grad();
+    VectorXd g = adj(alpha);
+    const double gb = beta0.adj();
+    set_zero_all_adjoints();
+    var lp_ref = gamma_lpdf_reference_cpu<false>(d.y_pos, alpha, beta0);
+    lp_ref.grad();
+    expect_rel(lp.val(), lp_ref.val(), std::fabs(lp_ref.val()), "gamma, var shape vector: value");
+    expect_rel(gb, beta0.adj(), std::fabs(beta0.adj()), "gamma, var shape vector: d/dbeta");
+    for (int i = 0; i < n; ++i) {
+      const double terms = std::fabs(digamma(al_d[i])) + std::fabs(std::log(1.3)) + std::fabs(std::log(d.y_pos[i]));
+      EXPECT_LE(std::fabs(g[i] - alpha[i].adj()), 1e-10 * std::max(std::fabs(alpha[i].adj()), terms)) << "gamma d/dalpha " << i;
+    }
+    set_zero_all_adjoints();
+  }
+  const double v = gamma_lpdf(d.y_pos, al_d, d.sigma);
+  expect_rel(v, gamma_lpdf_reference_cpu<false>(d.y_pos, al_d, d.sigma), std::fabs(v), "gamma, all double");
+  EXPECT_EQ(0.0, gamma_lpdf<true>(d.y_pos, al_d, d.sigma));
+  STAN_CUDA_PARITY("exponential, var vectors", exponential_lpdf(y, beta), exponential_lpdf_reference_cpu<false>(y, beta), adj(y),
+                   adj(beta));
+  STAN_CUDA_PARITY("exponential, the model statement", exponential_lpdf(d.y_pos, beta0), exponential_lpdf_reference_cpu<false>(d.y_pos, beta0),
+                   adj(beta0));
+  STAN_CUDA_PARITY("exponential propto, var y only", exponential_lpdf<true>(y, d.sigma), exponential_lpdf_reference_cpu<true>(y, d.sigma),
+                   adj(y));
+  const double w = exponential_lpdf(d.y_pos, d.sigma);
+  expect_rel(w, exponential_lpdf_reference_cpu<false>(d.y_pos, d.sigma), std::fabs(w), "exponential, all double");
+  EXPECT_EQ(0.0, exponential_lpdf<true>(d.y_pos, d.sigma));
+  stan::math::recover_memory();
+}
+
 INSTANTIATE_TEST_CASE_P(Sizes, CudaLocScale, ::testing::Values(1, 3, 1000, 100003));
+
+TEST(CudaLocScaleErrors, gamma_and_exponential_same_exceptions_and_log_zero_as_the_reference) {
+  using namespace stan::math;  // NOLINT
+  const int n = 2000;
+  Data d = make(n, 8);
+  VectorXd al_d = d.sigma.array() + 0.2;
+  vector_v alpha = to_v(al_d), beta = to_v(d.sigma);
+  VectorXd y_nan = d.y_pos, y_neg = d.y_pos;
+  y_nan[1999] = NAN;
+  y_neg[5] = -0.5;
+  vector_v alpha_zero = to_v(al_d), beta_inf = to_v(d.sigma);
+  alpha_zero[17] = 0.0;
+  beta_inf[9] = INFINITY;
+  EXPECT_THROW(gamma_lpdf(y_nan, alpha, beta), std::domain_error);
+  EXPECT_THROW(gamma_lpdf(d.y_pos, alpha_zero, beta), std::domain_error);
+  EXPECT_THROW(gamma_lpdf(d.y_pos, alpha, beta_inf), std::domain_error);
+  EXPECT_THROW(exponential_lpdf(y_nan, beta), std::domain_error);
+  EXPECT_THROW(exponential_lpdf(y_neg, beta), std::domain_error);
+  EXPECT_THROW(exponential_lpdf(d.y_pos, beta_inf), std::domain_error);
+  vector_v shorter = to_v(d.sigma.head(n - 1));
+  EXPECT_THROW(gamma_lpdf(d.y_pos, alpha, shorter), std::invalid_argument);
+  EXPECT_THROW(exponential_lpdf(d.y_pos, shorter), std::invalid_argument);
+  std::string m_gpu, m_cpu;
+  try {
+    gamma_lpdf(d.y_pos, alpha_zero, beta);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    gamma_lpdf_reference_cpu<false>(d.y_pos, alpha_zero, beta);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  m_gpu.clear();
+  m_cpu.clear();
+  try {
+    exponential_lpdf(y_neg, beta);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    exponential_lpdf_reference_cpu<false>(y_neg, beta);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  // a negative outcome: LOG_ZERO (gamma_lpdf.hpp:69-74)
+  EXPECT_EQ(LOG_ZERO, gamma_lpdf(y_neg, alpha, beta).val());
+  EXPECT_EQ(LOG_ZERO, gamma_lpdf_reference_cpu<false>(y_neg, alpha, beta).val());
+  VectorXd none(0);
+  vector_v empty(0);
+  EXPECT_EQ(0.0, gamma_lpdf(none, empty, empty).val());
+  EXPECT_EQ(0.0, exponential_lpdf(none, empty).val());
+  stan::math::recover_memory();
+}
 
 TEST(CudaLocScaleErrors, same_exceptions_and_log_zero_as_the_reference) {
   using namespace stan::math;  // NOLINT

@@ -90,6 +90,9 @@ static_assert(std::is_same<decltype(stan::math::bernoulli_logit_lpmf(ints(), vec
 static_assert(std::is_same<decltype(stan::math::poisson_log_lpmf(ints(), vector_fd())), fvar<double>>::value, "");
 static_assert(std::is_same<decltype(stan::math::poisson_lpmf(ints(), vector_v())), var>::value, "");
 static_assert(std::is_same<decltype(stan::math::cauchy_lpdf(vector_d(), vector_v(), 1.0)), var>::value, "");
+static_assert(std::is_same<decltype(stan::math::gamma_lpdf(vector_d(), var(), vector_v())), var>::value, "");
+static_assert(std::is_same<decltype(stan::math::exponential_lpdf(vector_d(), vector_fd())), fvar<double>>::value, "");
+static_assert(std::is_same<decltype(stan::math::exponential_lpdf<true>(vector_v(), 1.5)), var>::value, "");
 static_assert(std::is_same<decltype(stan::math::lognormal_lpdf<true>(vector_d(), vector_d(), 1.0)), double>::value, "");
 static_assert(std::is_same<decltype(stan::math::lognormal_lpdf(vector_d(), vector_fd(), 1.0)), fvar<double>>::value, "");
 static_assert(std::is_same<decltype(stan::math::poisson_lpmf<true>(ints(), vector_d())), double>::value, "");

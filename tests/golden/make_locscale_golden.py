@@ -1,6 +1,6 @@
 """Generates tests/golden/locscale_golden.npz from the UNMODIFIED reference (oracle/_ref/libstanref.so, compiled from
-/root/reference by oracle/Makefile): cauchy_lpdf(y | mu, sigma) and lognormal_lpdf(y | mu, sigma), value + reverse-mode
-gradient, for
+/root/reference by oracle/Makefile): cauchy_lpdf(y | mu, sigma), lognormal_lpdf(y | mu, sigma), gamma_lpdf(y | alpha, beta) and
+exponential_lpdf(y | beta), value + reverse-mode gradient, for
   * the reference's known-answer triples (test/prob/cauchy/cauchy_test.hpp:10-31,
     test/prob/lognormal/lognormal_test.hpp:10-25; the literal expected log-densities stored beside the output),
   * every subset of {y, mu, sigma} as autodiff variables x propto on one seeded vector case (the summands the
@@ -60,6 +60,31 @@ for density, yy, mm in (("cauchy", z, mu), ("lognormal", yl, mul)):
     add(density + "_scalar_y", density, yy[:1] if density == "cauchy" else [2.5], mm[:n], sg[:n], var_mask=0b111)
     add(density + "_scalar_sigma", density, yy[:n], mm[:n], [0.8], var_mask=0b110)
     add(density + "_scalar_mu", density, yy[:n], [-0.4], sg[:n], var_mask=0b011)
+
+# gamma_lpdf(y | alpha, beta) (alpha in the mu slot, beta in the sigma slot) and exponential_lpdf(y | beta) (beta in the
+# sigma slot, the mu slot holds one zero): known answers of test/prob/gamma/gamma_test.hpp:14-31 and
+# test/prob/exponential/exponential_test.hpp:14-28, every subset of variables x propto, scalar / vector operands, corners
+for i, (y, al, be, ka) in enumerate([(1.0, 2.0, 2.0, -0.6137056388801093165242), (2.0, 0.25, 0.75, -3.379803428230981676705),
+                                     (1.0, 1.0, 1.0, -1.0)]):
+    add("gamma_ka%d" % i, "gamma", [y], [al], [be], var_mask=0b111, known_answer=ka)
+for i, (y, be, ka) in enumerate([(2.0, 1.5, -2.594534891891835393096), (15.0, 3.9, -57.13902344686439249699),
+                                 (1e-08, 3.9, 1.3609765141356007)]):
+    add("exponential_ka%d" % i, "exponential", [y], [0.0], [be], var_mask=0b101, known_answer=ka)
+yg = np.concatenate([rng.gamma(2.0, 1.5, n), [1e-300, 1e-8, 1e8, 0.5, 3.0, 700.0]])
+al = np.concatenate([rng.uniform(0.2, 8.0, n), [1e-3, 0.5, 150.0, 1.0, 1.4616321449683623, 30.0]])
+be = np.concatenate([rng.uniform(0.3, 3.0, n), [1e-3, 1e3, 1e-6, 2.0, 1.0, 0.05]])
+for var_mask in range(8):
+    for propto in (False, True):
+        add("gamma_vec_m%d%s" % (var_mask, "_propto" if propto else ""), "gamma", yg, al, be, propto=propto, var_mask=var_mask)
+        if not var_mask & 2:
+            add("exponential_vec_m%d%s" % (var_mask, "_propto" if propto else ""), "exponential", yg, [0.0], be, propto=propto,
+                var_mask=var_mask)
+add("gamma_scalar_alpha_beta", "gamma", yg[:n], [2.2], [1.3], var_mask=0b111)
+add("gamma_scalar_y", "gamma", [2.5], al[:n], be[:n], var_mask=0b111)
+add("gamma_scalar_beta", "gamma", yg[:n], al[:n], [0.8], var_mask=0b110)
+add("gamma_zero_outcome", "gamma", [0.0, 1.0, 2.0], [2.0, 0.5, 1.0], [1.0], var_mask=0b110)   # log_y stays 0 (:86-90)
+add("exponential_scalar_beta", "exponential", yg[:n], [0.0], [1.3], var_mask=0b101)
+add("exponential_scalar_y", "exponential", [2.5], [0.0], be[:n], var_mask=0b101)
 
 out["cases"] = np.array(names)
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "locscale_golden.npz")

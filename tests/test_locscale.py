@@ -1,4 +1,4 @@
-"""cauchy_lpdf / lognormal_lpdf (and normal_lpdf through the same entry point) on the device
+"""cauchy_lpdf / lognormal_lpdf / gamma_lpdf / exponential_lpdf (and normal_lpdf through the same entry point) on the device
 (stan_cuda_locscale_lpdf_eval, csrc/normal_lpdf.cu): the plain-C oracle against the golden vectors of the compiled
 reference (CPU), and the CUDA path against both (GPU).  Bar: 1e-10 relative on the log-density and on every partial."""
 import numpy as np
@@ -32,11 +32,30 @@ def ls_case(g, name):
     return c
 
 
+def gamma_dalpha_scale(y, alpha, beta, size):
+    """d/dalpha of gamma_lpdf is -digamma(alpha) + log(beta) + log(y) (gamma_lpdf.hpp:134-137): three O(1) terms that may
+    cancel, so the partial is accurate to a few ulp of their magnitudes, not of itself (the floor student_t's d/dnu has)."""
+    from scipy.special import digamma
+    y, alpha, beta = (np.asarray(v, float) for v in (y, alpha, beta))
+    with np.errstate(divide="ignore"):
+        terms = np.abs(digamma(alpha)) + np.abs(np.log(beta)) + np.abs(np.where(y > 0, np.log(np.where(y > 0, y, 1.0)), 0.0))
+    terms = np.broadcast_to(terms, (max(y.size, alpha.size, beta.size),))
+    return terms if size > 1 else np.array([terms.sum()])
+
+
+def check_gamma_dalpha(got, ref, c, what, rtol):
+    scale = np.maximum(np.abs(ref), gamma_dalpha_scale(c["y"], c["mu"], c["sigma"], ref.size))
+    err = np.abs(np.asarray(got, float) - ref) / scale
+    assert not (err > rtol).any(), "%s dmu: %d components off, worst %.3e" % (what, int((err > rtol).sum()), err.max())
+
+
 def check_case(r, c, what, rtol=1e-10):
     assert r["rc"] == 0, what
     assert_close(r["lp"], c["lp"], what + " lp", rtol)
     for k, bit in KEYS:
-        if c["var_mask"] & bit:
+        if c["var_mask"] & bit and k == "dmu" and c.get("density") == _abi.LOCSCALE_GAMMA:
+            check_gamma_dalpha(r[k], np.asarray(c[k], float), c, what, rtol)
+        elif c["var_mask"] & bit:
             assert_close(r[k], c[k], what + " " + k, rtol)
             # element by element: relative to the element, floored at 1e-8 of the largest one
             ref, got = np.asarray(c[k], float), np.asarray(r[k], float)
@@ -49,7 +68,7 @@ def check_case(r, c, what, rtol=1e-10):
 def test_oracle_matches_golden_and_known_answers(golden_ls):
     """outputs of the compiled reference and the literal expected values of test/prob/cauchy/cauchy_test.hpp:10-31,
     test/prob/lognormal/lognormal_test.hpp:10-25"""
-    assert len(golden_ls["cases"]) >= 45
+    assert len(golden_ls["cases"]) >= 81
     known = 0
     for name in golden_ls["cases"]:
         c = ls_case(golden_ls, str(name))
@@ -58,7 +77,7 @@ def test_oracle_matches_golden_and_known_answers(golden_ls):
         if "known_answer" in c:
             known += 1
             assert abs(r["lp"] - c["known_answer"]) <= 1e-13 * max(1.0, abs(c["known_answer"])), name
-    assert known == 5
+    assert known == 11   # 3 cauchy, 2 lognormal, 3 gamma, 3 exponential
 
 
 def test_oracle_codes():
@@ -71,6 +90,15 @@ def test_oracle_codes():
             assert L.oracle_locscale_lpdf(d, [1.0], [0.0], [sg])["rc"] == _abi.BAD_OPERAND
         assert L.oracle_locscale_lpdf(d, [np.nan], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
         assert L.oracle_locscale_lpdf(d, [], [], [])["lp"] == 0.0
+    for al in (0.0, -1.0, np.inf, -np.inf, np.nan):      # test/prob/gamma/gamma_test.hpp:36-61
+        assert L.oracle_locscale_lpdf("gamma", [1.0], [al], [1.0])["rc"] == _abi.BAD_OPERAND
+        assert L.oracle_locscale_lpdf("gamma", [1.0], [1.0], [al])["rc"] == _abi.BAD_OPERAND
+        assert L.oracle_locscale_lpdf("exponential", [1.0], [0.0], [al])["rc"] == _abi.BAD_OPERAND
+    assert L.oracle_locscale_lpdf("gamma", [np.nan], [1.0], [1.0])["rc"] == _abi.BAD_OPERAND
+    r = L.oracle_locscale_lpdf("gamma", [1.0, -0.5], [1.0], [1.0])
+    assert r["rc"] == _abi.LOG_ZERO and r["lp"] == -np.inf                                  # gamma_lpdf.hpp:69-74
+    for bad_y in (-10.0, np.nan):                       # test/prob/exponential/exponential_test.hpp:31-36
+        assert L.oracle_locscale_lpdf("exponential", [bad_y], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
     assert L.oracle_locscale_lpdf("lognormal", [-1.0], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
     r = L.oracle_locscale_lpdf("lognormal", [1.0, 0.0], [0.0], [1.0])
     assert r["rc"] == _abi.LOG_ZERO and r["lp"] == -np.inf
@@ -78,24 +106,44 @@ def test_oracle_codes():
     assert L.oracle_locscale_lpdf("normal", [1.0], [0.0], [np.inf])["rc"] in (0, _abi.NONFINITE)   # check_positive only
 
 
+def synth(density, n, rng):
+    """operands in the density's domain (gamma: mu holds the shape; exponential: mu is one zero)"""
+    y = rng.standard_normal(n) * 2
+    mu, sg = rng.standard_normal(n), rng.uniform(0.3, 3.0, n)
+    if density == "lognormal":
+        y = np.exp(y)
+    elif density in ("gamma", "exponential"):
+        y = rng.gamma(2.0, 1.5, n)
+        mu = rng.uniform(0.2, 8.0, n) if density == "gamma" else np.zeros(1)
+    return y, mu, sg
+
+
+def masks(density):
+    return (0, 1, 4, 5) if density == "exponential" else range(8)
+
+
+DENSITIES = ["normal", "cauchy", "lognormal", "gamma", "exponential"]
+
+
 @needs_ref
-@pytest.mark.parametrize("density", ["normal", "cauchy", "lognormal"])
+@pytest.mark.parametrize("density", DENSITIES)
 def test_oracle_vs_compiled_reference(density):
     rng = np.random.default_rng(5)
     n = 3000
-    y = rng.standard_normal(n) * 2
-    y = np.exp(y) if density == "lognormal" else y
-    mu, sg = rng.standard_normal(n), rng.uniform(0.3, 3.0, n)
-    for var_mask in range(8):
+    y, mu, sg = synth(density, n, rng)
+    for var_mask in masks(density):
         for propto in (False, True):
             for ops in ((y, mu, sg), (y, mu[:1], sg[:1]), (y[:1], mu, sg)):
                 ref = L.ref_locscale_lpdf(density, *ops, propto=propto, var_mask=var_mask)
                 got = L.oracle_locscale_lpdf(density, *ops, propto=propto, var_mask=var_mask)
                 assert got["rc"] == 0
                 assert_close(got["lp"], ref["lp"], "%s lp" % density, 1e-12)
+                c = {"y": ops[0], "mu": ops[1], "sigma": ops[2]}
                 for k, bit in KEYS:
-                    if var_mask & bit:
-                        assert_close(got[k], ref[k], "%s %s" % (density, k), 1e-12)
+                    if var_mask & bit and k == "dmu" and density == "gamma":
+                        check_gamma_dalpha(got[k], ref[k], c, "gamma", 1e-12)
+                    elif var_mask & bit:   # (a scalar operand's partial is a sum of n terms that may cancel: the parity bar)
+                        assert_close(got[k], ref[k], "%s %s" % (density, k), 1e-12 if np.size(ref[k]) > 1 else 1e-10)
 
 
 # ---- the CUDA path -------------------------------------------------------------------------------------------------
@@ -118,6 +166,8 @@ def test_device_matches_golden(glm, golden_ls):
         check_case(r, c, "cuda vs golden " + str(name))
         if "known_answer" in c:
             assert abs(r["lp"] - c["known_answer"]) <= 1e-12 * max(1.0, abs(c["known_answer"])), name
+        if c["density"] not in by_id:
+            continue
         lp, g = by_id[c["density"]](c["y"], c["mu"], c["sigma"], propto=c["propto"], var_mask=c["var_mask"])
         assert lp == r["lp"] or (c["propto"] and c["var_mask"] == 0 and lp == 0.0)
         for (key, bit), gname in zip(KEYS, ("y", "mu", "sigma")):
@@ -126,28 +176,29 @@ def test_device_matches_golden(glm, golden_ls):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("density", ["normal", "cauchy", "lognormal"])
+@pytest.mark.parametrize("density", DENSITIES)
 @pytest.mark.parametrize("n", [1, 2, 31, 1025, 100_003, 1_000_000])
 def test_device_against_oracle(glm, density, n):
     rng = np.random.default_rng(n + len(density))
-    y = rng.standard_normal(n) * 2
-    y = np.exp(y) if density == "lognormal" else y
-    mu, sg = rng.standard_normal(n), rng.uniform(0.3, 3.0, n)
-    for var_mask, propto in ((0b111, False), (0b110, True), (0b001, True), (0b000, False)):
+    y, mu, sg = synth(density, n, rng)
+    expo = density == "exponential"
+    for var_mask, propto in ((0b101 if expo else 0b111, False), (0b100 if expo else 0b110, True), (0b001, True), (0b000, False)):
         flags = glm.locscale_flags(density, propto, var_mask)
         ref = L.oracle_locscale_lpdf(density, y, mu, sg, flags=flags)
         got = glm.locscale_eval(density, y, mu, sg, flags, y_is_data=not (var_mask & 1))
-        c = dict(ref, var_mask=var_mask)
+        c = dict(ref, var_mask=var_mask, density=_abi.LOCSCALES[density], y=y, mu=mu, sigma=sg)
         check_case(got, c, "%s n=%d mask=%d propto=%d" % (density, n, var_mask, propto))
-    flags = glm.locscale_flags(density, False, 0b111)
+    full = 0b101 if expo else 0b111
+    flags = glm.locscale_flags(density, False, full)
     first = glm.locscale_eval(density, y, mu, sg, flags, y_is_data=False)
     again = glm.locscale_eval(density, y, mu, sg, flags, y_is_data=False)
-    assert first["lp"] == again["lp"] and all(np.array_equal(first[k], again[k]) for k, _ in KEYS)   # fixed summation order
+    assert first["lp"] == again["lp"] and all(np.array_equal(first[k], again[k]) for k, b in KEYS if full & b)   # fixed summation order
     # scalar operands: their partials are sums over the elements
     for ops in ((y, mu[:1], sg[:1]), (y[:1], mu, sg), (y, mu, sg[:1])):
         ref = L.oracle_locscale_lpdf(density, *ops, flags=flags)
         got = glm.locscale_eval(density, *ops, flags, y_is_data=False)
-        check_case(got, dict(ref, var_mask=0b111), "%s scalar operands n=%d" % (density, n))
+        check_case(got, dict(ref, var_mask=full, density=_abi.LOCSCALES[density], y=ops[0], mu=ops[1], sigma=ops[2]),
+                   "%s scalar operands n=%d" % (density, n))
 
 
 @pytest.mark.gpu
@@ -180,4 +231,55 @@ def test_device_error_contract(glm):
     assert lp == -np.inf and g == {}
     assert glm.lognormal_lpdf(yz, mu, sg, propto=True, var_mask=0)[0] == -np.inf
     with pytest.raises(Exception):
-        glm.locscale_eval(3, y, mu, sg, glm.locscale_flags("cauchy"))
+        glm.locscale_eval(9, y, mu, sg, glm.locscale_flags("cauchy"))
+
+
+@pytest.mark.gpu
+def test_device_gamma_and_exponential_wrappers(glm, golden_ls):
+    """glm.gamma_lpdf / glm.exponential_lpdf against the golden vectors, and their error contract
+    (gamma_lpdf.hpp:48-74, exponential_lpdf.hpp:48-58; the invalid values of the reference's fixtures)"""
+    for name in golden_ls["cases"]:
+        c = ls_case(golden_ls, str(name))
+        if c["density"] == _abi.LOCSCALE_GAMMA:
+            lp, g = glm.gamma_lpdf(c["y"], c["mu"], c["sigma"], propto=c["propto"], var_mask=c["var_mask"])
+            keys = (("y", "dy", 1), ("alpha", "dmu", 2), ("beta", "dsigma", 4))
+        elif c["density"] == _abi.LOCSCALE_EXPONENTIAL:
+            vm2 = (c["var_mask"] & 1) | ((c["var_mask"] & 4) >> 1)
+            lp, g = glm.exponential_lpdf(c["y"], c["sigma"], propto=c["propto"], var_mask=vm2)
+            keys = (("y", "dy", 1), ("beta", "dsigma", 4))
+        else:
+            continue
+        assert_close(lp, c["lp"], "wrapper vs golden %s lp" % name)
+        for gname, key, bit in keys:
+            if c["var_mask"] & bit:
+                assert_close(g[gname], c[key], "wrapper vs golden %s %s" % (name, key))
+    n = 3000
+    y, al, be = np.linspace(0.1, 5, n), np.linspace(0.5, 4, n), np.linspace(0.5, 2, n)
+    for bad_value in (0.0, -1.0, np.inf, np.nan):
+        for k in (1, 2):
+            ops = [y.copy(), al.copy(), be.copy()]
+            ops[k][1234] = bad_value
+            with pytest.raises(glm.DomainError):
+                glm.gamma_lpdf(*ops)
+            assert glm.locscale_eval("gamma", *ops, glm.locscale_flags("gamma"), y_is_data=False)["rc"] == _abi.BAD_OPERAND
+        bb = be.copy()
+        bb[7] = bad_value
+        with pytest.raises(glm.DomainError):
+            glm.exponential_lpdf(y, bb)
+        assert glm.locscale_eval("exponential", y, [0.0], bb, glm.locscale_flags("exponential", False, 0b100),
+                                 y_is_data=False)["rc"] == _abi.BAD_OPERAND
+    yn = y.copy()
+    yn[5] = -0.5
+    lp, g = glm.gamma_lpdf(yn, al, be)                       # a negative outcome: LOG_ZERO, no partials (:69-74)
+    assert lp == -np.inf and g == {}
+    with pytest.raises(glm.DomainError):
+        glm.exponential_lpdf(yn, be)
+    ynan = y.copy()
+    ynan[5] = np.nan
+    with pytest.raises(glm.DomainError):
+        glm.gamma_lpdf(ynan, al, be)
+    with pytest.raises(ValueError) as e:
+        glm.gamma_lpdf(y[:10], al[:9], be[:10])
+    assert not isinstance(e.value, glm.DomainError)
+    assert glm.gamma_lpdf([], [], [])[0] == 0.0 and glm.exponential_lpdf([], [])[0] == 0.0
+    assert glm.gamma_lpdf(y, al, be, propto=True, var_mask=0)[0] == 0.0
