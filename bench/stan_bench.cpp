@@ -9,7 +9,7 @@
 // nested tape that is recovered afterwards; var construction is outside the timed region on both
 // sides.  X and y are cached on the device by the first (untimed) GPU evaluation.
 //
-//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|d3|d4|l1|l2|l3|l4|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
+//   stan_bench --config c1|c2|c3|c4|c5|d1|d2|d3|d4|l1|l2|l3|l4|l5|l6|s1|m1|m2|k1|k2|v2 [--n ROWS] [--reps R] [--cpu-reps R] [--threads T] [--no-cpu]
 // prints one JSON line: GPU evals/s (median), CPU single-thread and TBB map_rect evals/s, parity.
 #include <stan/math.hpp>
 
@@ -373,6 +373,8 @@ double locscale_once(const VectorXd& y, const VectorXd& mu_val, double sigma_val
   var lp = DENSITY == 1   ? (GPU ? cauchy_lpdf(y, mu, sigma) : cauchy_lpdf_reference_cpu<false>(y, mu, sigma))
            : DENSITY == 2 ? (GPU ? lognormal_lpdf(y, mu, sigma) : lognormal_lpdf_reference_cpu<false>(y, mu, sigma))
            : DENSITY == 3 ? (GPU ? gamma_lpdf(y, sigma, mu) : gamma_lpdf_reference_cpu<false>(y, sigma, mu))
+           : DENSITY == 5 ? (GPU ? beta_lpdf(y, sigma, mu) : beta_lpdf_reference_cpu<false>(y, sigma, mu))
+           : DENSITY == 6 ? (GPU ? weibull_lpdf(y, sigma, mu) : weibull_lpdf_reference_cpu<false>(y, sigma, mu))
                           : (GPU ? exponential_lpdf(y, mu) + 0.0 * sigma : exponential_lpdf_reference_cpu<false>(y, mu) + 0.0 * sigma);
   grad(lp.vi_);
   out->lp = lp.val();
@@ -591,7 +593,7 @@ int run(int argc, char** argv) {
     return 0;
   }
 
-  if (config == "l1" || config == "l2" || config == "l3" || config == "l4") {  // cauchy, lognormal, gamma, exponential
+  if (config.size() == 2 && config[0] == 'l' && config[1] >= '1' && config[1] <= '6') {  // cauchy, lognormal, gamma, exponential, beta, weibull
     const int which = config[1] - '0';
     const bool cauchy = which == 1;
     const int64_t n = n_override ? n_override : 1000000;
@@ -599,21 +601,25 @@ int run(int argc, char** argv) {
     Rng r(1040 + which);
     for (int64_t i = 0; i < n; ++i) {
       y[i] = cauchy ? 2.0 * r.normal() : std::exp(1.2 * r.normal());
-      mu[i] = which >= 3 ? std::exp(0.3 * r.normal()) : 0.1 * r.normal();   // gamma / exponential: positive rates
+      if (which == 5) y[i] = std::min(std::max(y[i] / (1.0 + y[i]), 1e-9), 1.0 - 1e-9);   // beta: outcomes in (0, 1)
+      mu[i] = which >= 3 ? std::exp(0.3 * r.normal()) : 0.1 * r.normal();   // gamma / exponential / beta / weibull: positive
     }
     Result g, c;
     auto gpu = [&] {
       return which == 1 ? locscale_once<true, 1>(y, mu, 1.3, &g) : which == 2 ? locscale_once<true, 2>(y, mu, 1.3, &g)
-             : which == 3 ? locscale_once<true, 3>(y, mu, 1.3, &g) : locscale_once<true, 4>(y, mu, 1.3, &g);
+             : which == 3 ? locscale_once<true, 3>(y, mu, 1.3, &g) : which == 4 ? locscale_once<true, 4>(y, mu, 1.3, &g)
+             : which == 5 ? locscale_once<true, 5>(y, mu, 1.3, &g) : locscale_once<true, 6>(y, mu, 1.3, &g);
     };
     auto cpu = [&] {
       return which == 1 ? locscale_once<false, 1>(y, mu, 1.3, &c) : which == 2 ? locscale_once<false, 2>(y, mu, 1.3, &c)
-             : which == 3 ? locscale_once<false, 3>(y, mu, 1.3, &c) : locscale_once<false, 4>(y, mu, 1.3, &c);
+             : which == 3 ? locscale_once<false, 3>(y, mu, 1.3, &c) : which == 4 ? locscale_once<false, 4>(y, mu, 1.3, &c)
+             : which == 5 ? locscale_once<false, 5>(y, mu, 1.3, &c) : locscale_once<false, 6>(y, mu, 1.3, &c);
     };
     gpu();
     Timing tg = time_reps(3, reps, 30, gpu);
-    static const char* names[5] = {"", "cauchy_lpdf N=%lld, y data, mu var vector, sigma var", "lognormal_lpdf N=%lld, y data, mu var vector, sigma var",
-                                   "gamma_lpdf N=%lld, y data, alpha var, beta var vector", "exponential_lpdf N=%lld, y data, beta var vector"};
+    static const char* names[7] = {"", "cauchy_lpdf N=%lld, y data, mu var vector, sigma var", "lognormal_lpdf N=%lld, y data, mu var vector, sigma var",
+                                   "gamma_lpdf N=%lld, y data, alpha var, beta var vector", "exponential_lpdf N=%lld, y data, beta var vector",
+                                   "beta_lpdf N=%lld, y data, alpha var, beta var vector", "weibull_lpdf N=%lld, y data, alpha var, sigma var vector"};
     std::printf("\"what\": \"");
     std::printf(names[which], (long long)n);
     std::printf("\", ");

@@ -194,6 +194,13 @@ typedef struct stan_cuda_normal_args {
  *     (exponential_lpdf.hpp:76-81): LP_SCALE = log(beta), LP_MAIN = -beta * y. */
 #define STAN_CUDA_LOCSCALE_GAMMA 3       /* prim/scal/prob/gamma_lpdf.hpp:41-145 */
 #define STAN_CUDA_LOCSCALE_EXPONENTIAL 4 /* prim/scal/prob/exponential_lpdf.hpp:42-95 */
+/*   beta_lpdf(y | alpha, beta): alpha in mu / dmu, beta in sigma / dsigma.  Summands (beta_lpdf.hpp:150-164):
+ *     LP_SCALE = lgamma(alpha + beta), LP_DOF = -lgamma(alpha), LP_LINEAR = -lgamma(beta), LP_Y = (alpha - 1) * log(y),
+ *     LP_MAIN = (beta - 1) * log1m(y).
+ *   weibull_lpdf(y | alpha, sigma): alpha in mu / dmu.  Summands (weibull_lpdf.hpp:111-123): LP_DOF = log(alpha),
+ *     LP_Y = (alpha - 1) * log(y), LP_SCALE = -alpha * log(sigma), LP_MAIN = -(y / sigma)^alpha. */
+#define STAN_CUDA_LOCSCALE_BETA 5        /* prim/scal/prob/beta_lpdf.hpp:40-181 */
+#define STAN_CUDA_LOCSCALE_WEIBULL 6     /* prim/scal/prob/weibull_lpdf.hpp:29-143 */
 /* lognormal only: the -sum log(y) term, which the reference ties to include_summand<propto, T_y>
  * (lognormal_lpdf.hpp:113-115) */
 #define STAN_CUDA_LP_Y 0x1000u
@@ -333,7 +340,9 @@ STAN_CUDA_API int stan_cuda_normal_lpdf_eval(const stan_cuda_normal_args* a);
  * eager checks throw (cauchy_lpdf.hpp:47-49: y NaN, mu not finite, sigma not positive and finite; lognormal_lpdf.hpp:24-27:
  * also y negative; gamma_lpdf.hpp:55-57: y NaN, alpha or beta not positive and finite; exponential_lpdf.hpp:55-56: y NaN or
  * negative, beta not positive and finite) and STAN_CUDA_LOG_ZERO for lognormal_lpdf with an outcome equal to zero (:41-45)
- * and gamma_lpdf with a negative outcome (gamma_lpdf.hpp:69-74). */
+ * and gamma_lpdf / weibull_lpdf with a negative outcome (gamma_lpdf.hpp:69-74, weibull_lpdf.hpp:56-61); beta_lpdf: either shape
+ * not positive and finite, y NaN or outside [0, 1] (beta_lpdf.hpp:48-54) and weibull_lpdf: y not finite, alpha or sigma not
+ * positive and finite (weibull_lpdf.hpp:38-40) are STAN_CUDA_BAD_OPERAND. */
 STAN_CUDA_API int stan_cuda_locscale_lpdf_eval(int32_t density, const stan_cuda_normal_args* a);
 /* Returns STAN_CUDA_BAD_OPERAND when an outcome is outside the density's support (bernoulli_logit: not in
  * {0, 1}, bernoulli_logit_lpmf.hpp:42; poisson_log: negative, poisson_log_lpmf.hpp:38) or the operand is NaN

@@ -21,6 +21,8 @@ struct NormalKernelParams {
 //   lognormal_lpdf  stan/math/prim/scal/prob/lognormal_lpdf.hpp:41-131
 //   gamma_lpdf      stan/math/prim/scal/prob/gamma_lpdf.hpp:69-145        (alpha in the mu slot, beta in the sigma slot)
 //   exponential_lpdf stan/math/prim/scal/prob/exponential_lpdf.hpp:55-90  (beta in the sigma slot, mu unused)
+//   beta_lpdf       stan/math/prim/scal/prob/beta_lpdf.hpp:48-177         (alpha in the mu slot, beta in the sigma slot)
+//   weibull_lpdf    stan/math/prim/scal/prob/weibull_lpdf.hpp:38-139      (alpha in the mu slot)
 template <int FAMILY, int THREADS>
 __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernelParams p) {
   const NormalIO& io = p.io;
@@ -45,7 +47,8 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
       if (lp_scale) log_sigma = log(sg);
     }
     bad |= isnan(y) ? 1u : 0u;
-    if (FAMILY == STAN_CUDA_LOCSCALE_GAMMA) bad |= (mu > 0.0 && isfinite(mu)) ? 0u : 2u;  // the shape: positive and finite
+    if (FAMILY == STAN_CUDA_LOCSCALE_GAMMA || FAMILY == STAN_CUDA_LOCSCALE_BETA || FAMILY == STAN_CUDA_LOCSCALE_WEIBULL)
+      bad |= (mu > 0.0 && isfinite(mu)) ? 0u : 2u;  // the shape: positive and finite
     else if (FAMILY != STAN_CUDA_LOCSCALE_EXPONENTIAL) bad |= isfinite(mu) ? 0u : 2u;
     if (io.sigma_vec) bad |= (sg > 0.0 && (FAMILY == STAN_CUDA_LOCSCALE_NORMAL || isfinite(sg))) ? 0u : 4u;
     double lp = 0.0, d_mu, d_sigma, d_y;
@@ -81,6 +84,33 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
       d_y = (mu - 1.0) / y - sg;                                         // :131-133
       d_mu = (io.flags & STAN_CUDA_NEED_DALPHA) ? -digamma_pos(mu) + log_beta + log_y : 0.0;  // :134-137
       d_sigma = mu / sg - y;                                             // :138-140
+    } else if (FAMILY == STAN_CUDA_LOCSCALE_BETA) {
+      // beta_lpdf.hpp:48-176 with alpha = mu, beta = sg; five summands, a flag each (include/stan_cuda.h)
+      bad |= (y < 0.0 || y > 1.0) ? 1u : 0u;           // :53-54 check_nonnegative / check_less_or_equal(y, 1)
+      const double log_y = log(y), log1m_y = log1p(-y);                  // :87-94
+      const bool want_dig = (io.flags & (STAN_CUDA_NEED_DALPHA | STAN_CUDA_NEED_DSIGMA)) != 0;
+      const double dig_ab = want_dig ? digamma_pos(mu + sg) : 0.0;       // :131-141
+      if (lp_scale) lp += lgamma(mu + sg);                               // :150-152
+      if (io.flags & STAN_CUDA_LP_DOF) lp -= lgamma(mu);                 // :153-155
+      if (io.flags & STAN_CUDA_LP_LINEAR) lp -= lgamma(sg);              // :156-158
+      if (lp_y) lp += (mu - 1.0) * log_y;                                // :159-161
+      if (lp_main) lp += (sg - 1.0) * log1m_y;                           // :162-164
+      d_y = (mu - 1.0) / y + (sg - 1.0) / (y - 1.0);                     // :166-169
+      d_mu = (io.flags & STAN_CUDA_NEED_DALPHA) ? log_y + dig_ab - digamma_pos(mu) : 0.0;      // :170-173
+      d_sigma = (io.flags & STAN_CUDA_NEED_DSIGMA) ? log1m_y + dig_ab - digamma_pos(sg) : 0.0;  // :174-177
+    } else if (FAMILY == STAN_CUDA_LOCSCALE_WEIBULL) {
+      // weibull_lpdf.hpp:38-139 with alpha = mu, sigma = sg
+      bad |= isfinite(y) ? 0u : 1u;                    // :38 check_finite(y)
+      bad |= (y < 0.0) ? 8u : 0u;                      // :56-61 LOG_ZERO
+      const double log_y = log(y), log_sg = log(sg), inv_y = 1.0 / y;
+      const double pw = pow(y * inv_sigma, mu);        // :95-103
+      if (io.flags & STAN_CUDA_LP_DOF) lp += log(mu);                    // :111-113
+      if (lp_y) lp += (mu - 1.0) * log_y;                                // :114-116
+      if (lp_scale) lp -= mu * log_sg;                                   // :117-119
+      if (lp_main) lp -= pw;                                             // :120-122
+      d_y = (mu - 1.0) * inv_y - mu * pw * inv_y;                        // :125-130
+      d_mu = 1.0 / mu + (1.0 - pw) * (log_y - log_sg);                   // :131-135
+      d_sigma = mu * inv_sigma * (pw - 1.0);                             // :136-139
     } else if (FAMILY == STAN_CUDA_LOCSCALE_EXPONENTIAL) {
       bad |= (y < 0.0) ? 1u : 0u;                      // exponential_lpdf.hpp:55 check_nonnegative(y)
       if (lp_scale) lp += log(sg);                     // :76-78
@@ -189,6 +219,12 @@ int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream
       break;
     case STAN_CUDA_LOCSCALE_EXPONENTIAL:
       normal_lpdf_kernel<STAN_CUDA_LOCSCALE_EXPONENTIAL, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_LOCSCALE_BETA:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_BETA, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_LOCSCALE_WEIBULL:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_WEIBULL, THREADS><<<grid, THREADS, 0, stream>>>(p);
       break;
     default:
       return fail(STAN_CUDA_ERR_ARG, "launch_normal_lpdf: unknown density");

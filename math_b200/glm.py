@@ -501,6 +501,14 @@ def locscale_flags(density, propto=False, var_mask=0b110):
         f |= (_abi.LP_DOF if (not propto or vm) else 0) | (_abi.LP_SCALE if (not propto or vm or vs) else 0)
         f |= (_abi.LP_Y if (not propto or vy or vm) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
         return f
+    if d == _abi.LOCSCALE_BETA:         # beta_lpdf.hpp:150-164 (alpha = the mu operand, beta = the sigma operand)
+        f |= (_abi.LP_SCALE if (not propto or vm or vs) else 0) | (_abi.LP_DOF if (not propto or vm) else 0)
+        f |= (_abi.LP_LINEAR if (not propto or vs) else 0) | (_abi.LP_Y if (not propto or vy or vm) else 0)
+        return f | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
+    if d == _abi.LOCSCALE_WEIBULL:      # weibull_lpdf.hpp:111-123 (alpha = the mu operand)
+        f |= (_abi.LP_DOF if (not propto or vm) else 0) | (_abi.LP_Y if (not propto or vy or vm) else 0)
+        f |= (_abi.LP_SCALE if (not propto or vm or vs) else 0)
+        return f | (_abi.LP_MAIN if (not propto or vy or vm or vs) else 0)
     if d == _abi.LOCSCALE_EXPONENTIAL:  # exponential_lpdf.hpp:76-81 (beta = the sigma operand)
         f &= ~_abi.NEED_DALPHA
         return f | (_abi.LP_SCALE if (not propto or vs) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
@@ -551,6 +559,51 @@ def gamma_lpdf(y, alpha, beta, propto=False, var_mask=0b110, y_is_data=True):
     if r["rc"] == _abi.LOG_ZERO:
         return -np.inf, {}
     return r["lp"], {name: r[key] for name, key, bit in (("y", "dy", 1), ("alpha", "dmu", 2), ("beta", "dsigma", 4)) if var_mask & bit}
+
+
+def _shape_density(f, density, y, alpha, second, propto, var_mask, y_is_data, y_check, second_name, names, log_zero=None):
+    """beta_lpdf.hpp:48-60 / weibull_lpdf.hpp:38-49: domain errors, size error, nothing to compute -> 0."""
+    y, alpha, second = _f64(y), _f64(alpha), _f64(second)
+    if not np.all((alpha > 0) & np.isfinite(alpha)):
+        raise DomainError("%s: %s must be positive finite" % (f, "First shape parameter" if density == "beta" else "Shape parameter"))
+    if not np.all((second > 0) & np.isfinite(second)):
+        raise DomainError("%s: %s must be positive finite" % (f, second_name))
+    y_check(y)
+    if min(y.size, alpha.size, second.size) == 0:
+        return 0.0, {}
+    n = max(y.size, alpha.size, second.size)
+    for name, v in (("Random variable", y), ("Shape parameter", alpha), (second_name, second)):
+        if v.size != 1 and v.size != n:
+            raise ValueError("%s: %s has dimension = %d, expecting dimension = %d" % (f, name, v.size, n))
+    if propto and var_mask == 0:
+        return 0.0, {}
+    r = locscale_eval(density, y, alpha, second, locscale_flags(density, propto, var_mask), y_is_data=y_is_data and not (var_mask & 1))
+    if r["rc"] == _abi.BAD_OPERAND:
+        raise DomainError("%s: operand outside the domain" % f)
+    if r["rc"] == _abi.LOG_ZERO:
+        return -np.inf, {}
+    return r["lp"], {name: r[key] for name, key, bit in names if var_mask & bit}
+
+
+def beta_lpdf(y, alpha, beta, propto=False, var_mask=0b110, y_is_data=True):
+    """stan/math/prim/scal/prob/beta_lpdf.hpp:40-43; var_mask: which of y (bit 0), alpha (1), beta (2) are variables."""
+    def y_check(y):
+        if np.any(np.isnan(y)):
+            raise DomainError("beta_lpdf: Random variable is nan")
+        if not np.all((y >= 0) & (y <= 1)):
+            raise DomainError("beta_lpdf: Random variable must be in [0, 1]")
+    return _shape_density("beta_lpdf", "beta", y, alpha, beta, propto, var_mask, y_is_data, y_check, "Second shape parameter",
+                          (("y", "dy", 1), ("alpha", "dmu", 2), ("beta", "dsigma", 4)))
+
+
+def weibull_lpdf(y, alpha, sigma, propto=False, var_mask=0b110, y_is_data=True):
+    """stan/math/prim/scal/prob/weibull_lpdf.hpp:29-31; var_mask: which of y (bit 0), alpha (1), sigma (2) are variables;
+    a negative outcome is LOG_ZERO (:56-61)."""
+    def y_check(y):
+        if not np.all(np.isfinite(y)):
+            raise DomainError("weibull_lpdf: Random variable must be finite")
+    return _shape_density("weibull_lpdf", "weibull", y, alpha, sigma, propto, var_mask, y_is_data, y_check, "Scale parameter",
+                          (("y", "dy", 1), ("alpha", "dmu", 2), ("sigma", "dsigma", 4)))
 
 
 def exponential_lpdf(y, beta, propto=False, var_mask=0b10, y_is_data=True):

@@ -415,12 +415,70 @@ static int oracle_gamma_exponential(int density, const stan_cuda_normal_args* a)
   return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+/* beta_lpdf(y | alpha, beta) (stan/math/prim/scal/prob/beta_lpdf.hpp:40-181) and weibull_lpdf(y | alpha, sigma)
+ * (weibull_lpdf.hpp:29-143); alpha in the mu slot, beta / sigma in the sigma slot */
+static int oracle_beta_weibull(int density, const stan_cuda_normal_args* a) {
+  const int bet = density == STAN_CUDA_LOCSCALE_BETA;
+  for (int64_t i = 0; i < a->mu_len; ++i)
+    if (!(a->mu[i] > 0.0) || !isfinite(a->mu[i])) return STAN_CUDA_BAD_OPERAND;             /* beta :48, weibull :39 */
+  for (int64_t i = 0; i < a->sigma_len; ++i)
+    if (!(a->sigma[i] > 0.0) || !isfinite(a->sigma[i])) return STAN_CUDA_BAD_OPERAND;       /* :49 / :40 */
+  for (int64_t i = 0; i < a->y_len; ++i) {
+    if (bet && (isnan(a->y[i]) || a->y[i] < 0 || a->y[i] > 1)) return STAN_CUDA_BAD_OPERAND; /* :50, :53-54 */
+    if (!bet && !isfinite(a->y[i])) return STAN_CUDA_BAD_OPERAND;                           /* :38 */
+  }
+  if (!bet)
+    for (int64_t i = 0; i < a->y_len; ++i)
+      if (a->y[i] < 0) {                                                                    /* :56-61 */
+        if (a->lp) *a->lp = -INFINITY;
+        return STAN_CUDA_LOG_ZERO;
+      }
+  const int ym = a->y_len != 1, mm = a->mu_len != 1, sm = a->sigma_len != 1;
+  const int need_mu = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dmu;
+  const int need_sigma = (a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma;
+  const int need_y = (a->flags & STAN_CUDA_NEED_DY) && a->dy;
+  if (need_mu) for (int64_t i = 0; i < a->mu_len; ++i) a->dmu[i] = 0.0;
+  if (need_sigma) for (int64_t i = 0; i < a->sigma_len; ++i) a->dsigma[i] = 0.0;
+  if (need_y) for (int64_t i = 0; i < a->y_len; ++i) a->dy[i] = 0.0;
+  double logp = 0.0;
+  for (int64_t n = 0; n < a->n; ++n) {
+    const double y = a->y[ym ? n : 0], alpha = a->mu[mm ? n : 0], sg = a->sigma[sm ? n : 0];
+    if (bet) {
+      const double log_y = log(y), log1m_y = log1p(-y);                                     /* :87-94 */
+      if (a->flags & STAN_CUDA_LP_SCALE) logp += lgamma(alpha + sg);                        /* :150-152 */
+      if (a->flags & STAN_CUDA_LP_DOF) logp -= lgamma(alpha);                               /* :153-155 */
+      if (a->flags & STAN_CUDA_LP_LINEAR) logp -= lgamma(sg);                               /* :156-158 */
+      if (a->flags & STAN_CUDA_LP_Y) logp += (alpha - 1.0) * log_y;                         /* :159-161 */
+      if (a->flags & STAN_CUDA_LP_MAIN) logp += (sg - 1.0) * log1m_y;                       /* :162-164 */
+      if (need_y) a->dy[ym ? n : 0] += (alpha - 1) / y + (sg - 1) / (y - 1);                /* :166-169 */
+      if (need_mu) a->dmu[mm ? n : 0] += log_y + oracle_digamma(alpha + sg) - oracle_digamma(alpha);       /* :170-173 */
+      if (need_sigma) a->dsigma[sm ? n : 0] += log1m_y + oracle_digamma(alpha + sg) - oracle_digamma(sg);  /* :174-177 */
+    } else {
+      const double inv_sigma = 1.0 / sg, log_y = log(y), log_sigma = log(sg);
+      const double pw = pow(y * inv_sigma, alpha);                                          /* :95-103 */
+      if (a->flags & STAN_CUDA_LP_DOF) logp += log(alpha);                                  /* :111-113 */
+      if (a->flags & STAN_CUDA_LP_Y) logp += (alpha - 1.0) * log_y;                         /* :114-116 */
+      if (a->flags & STAN_CUDA_LP_SCALE) logp -= alpha * log_sigma;                         /* :117-119 */
+      if (a->flags & STAN_CUDA_LP_MAIN) logp -= pw;                                         /* :120-122 */
+      if (need_y) {
+        const double inv_y = 1.0 / y;
+        a->dy[ym ? n : 0] += (alpha - 1.0) * inv_y - alpha * pw * inv_y;                    /* :125-130 */
+      }
+      if (need_mu) a->dmu[mm ? n : 0] += 1.0 / alpha + (1.0 - pw) * (log_y - log_sigma);    /* :131-135 */
+      if (need_sigma) a->dsigma[sm ? n : 0] += alpha * inv_sigma * (pw - 1.0);              /* :136-139 */
+    }
+  }
+  if (a->lp) *a->lp = logp;
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
 int oracle_locscale_lpdf_eval(int density, const stan_cuda_normal_args* a) {
-  if (!a || a->n < 0 || density < STAN_CUDA_LOCSCALE_NORMAL || density > STAN_CUDA_LOCSCALE_EXPONENTIAL) return STAN_CUDA_ERR_ARG;
+  if (!a || a->n < 0 || density < STAN_CUDA_LOCSCALE_NORMAL || density > STAN_CUDA_LOCSCALE_WEIBULL) return STAN_CUDA_ERR_ARG;
   if (a->n == 0) {
     if (a->lp) *a->lp = 0.0;
     return STAN_CUDA_OK;
   }
+  if (density >= STAN_CUDA_LOCSCALE_BETA) return oracle_beta_weibull(density, a);
   if (density >= STAN_CUDA_LOCSCALE_GAMMA) return oracle_gamma_exponential(density, a);
   const int lognormal = density == STAN_CUDA_LOCSCALE_LOGNORMAL, normal = density == STAN_CUDA_LOCSCALE_NORMAL;
   for (int64_t i = 0; i < a->y_len; ++i)

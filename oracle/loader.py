@@ -393,6 +393,14 @@ def locscale_flags(density, propto=False, var_mask=0b110):
         f |= (_abi.LP_DOF if (not propto or vm) else 0) | (_abi.LP_SCALE if (not propto or vm or vs) else 0)
         f |= (_abi.LP_Y if (not propto or vy or vm) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
         return f
+    if d == _abi.LOCSCALE_BETA:         # beta_lpdf.hpp:150-164 (alpha = the mu operand, beta = the sigma operand)
+        f |= (_abi.LP_SCALE if (not propto or vm or vs) else 0) | (_abi.LP_DOF if (not propto or vm) else 0)
+        f |= (_abi.LP_LINEAR if (not propto or vs) else 0) | (_abi.LP_Y if (not propto or vy or vm) else 0)
+        return f | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
+    if d == _abi.LOCSCALE_WEIBULL:      # weibull_lpdf.hpp:111-123 (alpha = the mu operand)
+        f |= (_abi.LP_DOF if (not propto or vm) else 0) | (_abi.LP_Y if (not propto or vy or vm) else 0)
+        f |= (_abi.LP_SCALE if (not propto or vm or vs) else 0)
+        return f | (_abi.LP_MAIN if (not propto or vy or vm or vs) else 0)
     if d == _abi.LOCSCALE_EXPONENTIAL:  # exponential_lpdf.hpp:76-81 (beta = the sigma operand)
         f &= ~_abi.NEED_DALPHA
         return f | (_abi.LP_SCALE if (not propto or vs) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)

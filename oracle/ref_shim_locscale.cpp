@@ -94,6 +94,21 @@ struct Call<4, propto> {  // exponential_lpdf(y | beta): beta in the sigma slot,
   }
 };
 
+template <bool propto>
+struct Call<5, propto> {  // beta_lpdf(y | alpha, beta)
+  template <typename A, typename B, typename C>
+  static auto go(const A& y, const B& alpha, const C& beta) -> decltype(stan::math::beta_lpdf<propto>(y, alpha, beta)) {
+    return stan::math::beta_lpdf<propto>(y, alpha, beta);
+  }
+};
+template <bool propto>
+struct Call<6, propto> {  // weibull_lpdf(y | alpha, sigma)
+  template <typename A, typename B, typename C>
+  static auto go(const A& y, const B& alpha, const C& sigma) -> decltype(stan::math::weibull_lpdf<propto>(y, alpha, sigma)) {
+    return stan::math::weibull_lpdf<propto>(y, alpha, sigma);
+  }
+};
+
 // peel one operand at a time into its static type, then call the reference
 template <int FAMILY, bool propto, typename... Done>
 struct Dispatch {
@@ -123,7 +138,8 @@ double run_family(bool propto, const Operand& y, const Operand& mu, const Operan
 extern "C" {
 
 // density 0: normal_lpdf, 1: cauchy_lpdf, 2: lognormal_lpdf, 3: gamma_lpdf(y | alpha = mu, beta = sigma),
-// 4: exponential_lpdf(y | beta = sigma; pass mu as one double).  var_mask bit 0: y, bit 1: mu, bit 2: sigma.  Lengths are 1
+// 4: exponential_lpdf(y | beta = sigma; pass mu as one double), 5: beta_lpdf(y | alpha = mu, beta = sigma),
+// 6: weibull_lpdf(y | alpha = mu, sigma).  var_mask bit 0: y, bit 1: mu, bit 2: sigma.  Lengths are 1
 // (scalar) or n (vector).  Returns 0, or 1 (std::domain_error) / 2 (std::invalid_argument) / 3 (other) with the
 // exception text in err.
 int stanref_locscale_lpdf(int density, int propto, int var_mask, const double* y, long y_len, const double* mu, long mu_len,
@@ -137,7 +153,9 @@ int stanref_locscale_lpdf(int density, int propto, int var_mask, const double* y
     const double r = density == 0   ? run_family<0>(propto != 0, oy, om, os)
                      : density == 1 ? run_family<1>(propto != 0, oy, om, os)
                      : density == 2 ? run_family<2>(propto != 0, oy, om, os)
-                     : density == 3 ? run_family<3>(propto != 0, oy, om, os) : run_family<4>(propto != 0, oy, om, os);
+                     : density == 3 ? run_family<3>(propto != 0, oy, om, os)
+                     : density == 4 ? run_family<4>(propto != 0, oy, om, os)
+                     : density == 5 ? run_family<5>(propto != 0, oy, om, os) : run_family<6>(propto != 0, oy, om, os);
     auto t1 = std::chrono::steady_clock::now();
     if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
     if (lp) *lp = r;

@@ -3,6 +3,7 @@
 #ifdef STAN_CUDA
 
 #include <stan/math/cuda/normal_lpdf.hpp>
+#include <stan/math/prim/scal/err/check_less_or_equal.hpp>
 #include <stan/math/prim/scal/err/check_nonnegative.hpp>
 #include <stan/math/prim/scal/err/check_positive_finite.hpp>
 #include <stan/math/prim/scal/fun/constants.hpp>
@@ -14,7 +15,7 @@ namespace math {
 namespace cuda {
 
 /**
- * cauchy_lpdf, lognormal_lpdf, gamma_lpdf and exponential_lpdf on the device: the operands, their staging and the tape node are
+ * cauchy_lpdf, lognormal_lpdf, gamma_lpdf, exponential_lpdf, beta_lpdf and weibull_lpdf on the device: the operands, their staging and the tape node are
  * those of normal_lpdf_device (stan/math/cuda/normal_lpdf.hpp); the density id selects the per-element term of the
  * kernel (stan_cuda_locscale_lpdf_eval).  Eligible calls: the vectorised ones with something to compute -- when
  * include_summand<propto, T_y, T_loc, T_scale> is false the reference body only runs its checks, and stays in charge.
@@ -84,6 +85,37 @@ struct exponential_checks {
   }
 };
 
+/** the eager checks of beta_lpdf.hpp:48-54: the shapes and NaN outcomes, then (behind the size check) the range of y */
+struct beta_checks {
+  static const char* function() { return "beta_lpdf"; }
+  template <typename T_y, typename T_a, typename T_b>
+  static void run(const T_y& y, const T_a& alpha, const T_b& beta) {
+    check_positive_finite(function(), "First shape parameter", alpha);
+    check_positive_finite(function(), "Second shape parameter", beta);
+    check_not_nan(function(), "Random variable", y);
+  }
+  template <typename T_y, typename T_a, typename T_b>
+  static void sizes(const T_y& y, const T_a& alpha, const T_b& beta) {
+    check_consistent_sizes(function(), "Random variable", y, "First shape parameter", alpha, "Second shape parameter", beta);
+    check_nonnegative(function(), "Random variable", y);
+    check_less_or_equal(function(), "Random variable", y, 1);
+  }
+};
+/** the eager checks of weibull_lpdf.hpp:38-40 */
+struct weibull_checks {
+  static const char* function() { return "weibull_lpdf"; }
+  template <typename T_y, typename T_a, typename T_s>
+  static void run(const T_y& y, const T_a& alpha, const T_s& sigma) {
+    check_finite(function(), "Random variable", y);
+    check_positive_finite(function(), "Shape parameter", alpha);
+    check_positive_finite(function(), "Scale parameter", sigma);
+  }
+  template <typename T_y, typename T_a, typename T_s>
+  static void sizes(const T_y& y, const T_a& alpha, const T_s& sigma) {
+    check_consistent_sizes(function(), "Random variable", y, "Shape parameter", alpha, "Scale parameter", sigma);
+  }
+};
+
 /**
  * One vectorised evaluation: stages the operands, builds the tape node in place (arena_partials), calls the device.
  * summands: the STAN_CUDA_LP_* bits of the terms the reference keeps for these operand types under this propto.
@@ -142,6 +174,7 @@ return_type_t<T_y, T_loc, T_scale> locscale_lpdf_call(int density, uint32_t summ
   check_cuda_rc(function, rc);
   if (rc == STAN_CUDA_BAD_OPERAND) {
     Checks::run(y, mu, sigma);
+    Checks::sizes(y, mu, sigma);  // (the sizes agree here; beta_lpdf tests the range of y behind its size check)
     throw std::domain_error(std::string(function) + ": operand outside the domain (device check)");
   }
   if (rc == STAN_CUDA_LOG_ZERO) {
@@ -218,6 +251,44 @@ return_type_t<T_y, T_inv_scale> exponential_lpdf_device(const T_y& y, const T_in
                             | (include_summand<propto, T_y, T_inv_scale>::value ? STAN_CUDA_LP_MAIN : 0u);
   const double unused = 0.0;
   return detail::locscale_lpdf_call<detail::exponential_checks>(STAN_CUDA_LOCSCALE_EXPONENTIAL, summands, y, unused, beta);
+}
+
+/**
+ * GPU body of the vectorised beta_lpdf (reference: stan/math/prim/scal/prob/beta_lpdf.hpp:40-181): five summands, each
+ * under its own include_summand condition (:150-164), three digammas for the shape partials (:170-177).  The reference runs
+ * its checks before it looks at the sizes (:48-56).
+ */
+template <bool propto, typename T_y, typename T_scale_succ, typename T_scale_fail>
+return_type_t<T_y, T_scale_succ, T_scale_fail> beta_lpdf_device(const T_y& y, const T_scale_succ& alpha,
+                                                               const T_scale_fail& beta) {
+  if (size_zero(y, alpha, beta)) {
+    detail::beta_checks::run(y, alpha, beta);
+    detail::beta_checks::sizes(y, alpha, beta);
+    return 0.0;
+  }
+  const uint32_t summands = (include_summand<propto, T_scale_succ, T_scale_fail>::value ? STAN_CUDA_LP_SCALE : 0u)
+                            | (include_summand<propto, T_scale_succ>::value ? STAN_CUDA_LP_DOF : 0u)
+                            | (include_summand<propto, T_scale_fail>::value ? STAN_CUDA_LP_LINEAR : 0u)
+                            | (include_summand<propto, T_y, T_scale_succ>::value ? STAN_CUDA_LP_Y : 0u)
+                            | (include_summand<propto, T_y, T_scale_fail>::value ? STAN_CUDA_LP_MAIN : 0u);
+  return detail::locscale_lpdf_call<detail::beta_checks>(STAN_CUDA_LOCSCALE_BETA, summands, y, alpha, beta);
+}
+
+/**
+ * GPU body of the vectorised weibull_lpdf (reference: stan/math/prim/scal/prob/weibull_lpdf.hpp:29-143), including its
+ * LOG_ZERO for a negative outcome (:56-61).  Checks before sizes, as there (:38-45).
+ */
+template <bool propto, typename T_y, typename T_shape, typename T_scale>
+return_type_t<T_y, T_shape, T_scale> weibull_lpdf_device(const T_y& y, const T_shape& alpha, const T_scale& sigma) {
+  if (size_zero(y, alpha, sigma)) {
+    detail::weibull_checks::run(y, alpha, sigma);
+    detail::weibull_checks::sizes(y, alpha, sigma);
+    return 0.0;
+  }
+  const uint32_t summands = (include_summand<propto, T_shape>::value ? STAN_CUDA_LP_DOF : 0u)
+                            | (include_summand<propto, T_y, T_shape>::value ? STAN_CUDA_LP_Y : 0u)
+                            | (include_summand<propto, T_shape, T_scale>::value ? STAN_CUDA_LP_SCALE : 0u) | STAN_CUDA_LP_MAIN;
+  return detail::locscale_lpdf_call<detail::weibull_checks>(STAN_CUDA_LOCSCALE_WEIBULL, summands, y, alpha, sigma);
 }
 
 }  // namespace cuda

@@ -1,5 +1,5 @@
 // The reference's distribution-test fixture (test/prob/test_fixture_distr.hpp) and its cauchy and lognormal test
-// classes and those of gamma and exponential (test/prob/{cauchy,lognormal,gamma,exponential}/*_test.hpp: known answers,
+// classes and those of gamma, exponential, beta and weibull (test/prob/{cauchy,lognormal,gamma,exponential,beta,weibull}/*_test.hpp: known answers,
 // invalid values),
 // all included UNMODIFIED from the reference tree and instantiated -- the way the reference's generator
 // (test/prob/generate_tests.cpp:235-340) writes its "_v_" files -- for argument kinds the overlay routes to the
@@ -14,6 +14,8 @@
 #include <test/prob/lognormal/lognormal_test.hpp>
 #include <test/prob/gamma/gamma_test.hpp>
 #include <test/prob/exponential/exponential_test.hpp>
+#include <test/prob/beta/beta_test.hpp>
+#include <test/prob/weibull/weibull_test.hpp>
 #include <vector>
 
 typedef Eigen::Matrix<var, Eigen::Dynamic, 1> vector_var;
@@ -58,6 +60,23 @@ STAN_CUDA_DISTR(AgradDistributionsGamma, 4)
 STAN_CUDA_DISTR(AgradDistributionsGamma, 5)
 STAN_CUDA_DISTR(AgradDistributionsGamma, 6)
 STAN_CUDA_DISTR(AgradDistributionsGamma, 7)
+
+STAN_CUDA_DISTR(AgradDistributionsBeta, 0)
+STAN_CUDA_DISTR(AgradDistributionsBeta, 1)
+STAN_CUDA_DISTR(AgradDistributionsBeta, 2)
+STAN_CUDA_DISTR(AgradDistributionsBeta, 3)
+STAN_CUDA_DISTR(AgradDistributionsBeta, 4)
+STAN_CUDA_DISTR(AgradDistributionsBeta, 5)
+STAN_CUDA_DISTR(AgradDistributionsBeta, 6)
+STAN_CUDA_DISTR(AgradDistributionsBeta, 7)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 0)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 1)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 2)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 3)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 4)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 5)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 6)
+STAN_CUDA_DISTR(AgradDistributionsWeibull, 7)
 
 // exponential_lpdf(y | beta): two operands
 typedef boost::mpl::vector<std::vector<double>, var, empty, empty, empty, empty> type_e_0;   // data y, var rate: the model statement

@@ -1,4 +1,4 @@
-// cauchy_lpdf / lognormal_lpdf / gamma_lpdf / exponential_lpdf on the device through the reference's own C++ signatures, against the
+// cauchy_lpdf / lognormal_lpdf / gamma_lpdf / exponential_lpdf / beta_lpdf / weibull_lpdf on the device through the reference's own C++ signatures, against the
 // unmodified reference bodies (reachable in the same binary as *_reference_cpu, see overlay/), at the north star's
 // tolerance: every mix of var / double and vector / scalar operands that the overlay routes, propto on and off, the
 // reference's exceptions and its LOG_ZERO.
@@ -169,7 +169,139 @@ TEST_P(CudaLocScale, gamma_and_exponential_match_reference_loop) {
   stan::math::recover_memory();
 }
 
+// partials made of terms that may cancel (digamma differences, (1 - p)(log y - log sigma), ...) are compared against the
+// magnitude `floor` of those terms, like student_t's d/dnu (tests/test_locscale.py has the same gates)
+void expect_floor(double got, double ref, double floor, const char* what, int i) {
+  EXPECT_LE(std::fabs(got - ref), 1e-10 * std::max(std::fabs(ref), floor)) << what << " " << i << " got " << got << " ref " << ref;
+}
+
+TEST_P(CudaLocScale, beta_and_weibull_match_reference_loop) {
+  const int n = GetParam();
+  Data d = make(n, 400 + n);
+  using namespace stan::math;  // NOLINT
+  VectorXd yb(n), a_d = d.sigma.array() + 0.2, b_d = d.sigma.reverse().array() + 0.1;
+  for (int i = 0; i < n; ++i) yb[i] = std::min(std::max(1.0 / (1.0 + std::exp(-d.y[i])), 1e-9), 1.0 - 1e-9);
+  {
+    vector_v y = to_v(yb), alpha = to_v(a_d), beta = to_v(b_d);
+    var lp = beta_lpdf(y, alpha, beta);
+    lp.grad();
+    VectorXd gy = adj(y), ga = adj(alpha), gb = adj(beta);
+    set_zero_all_adjoints();
+    var lp_ref = beta_lpdf_reference_cpu<false>(y, alpha, beta);
+    lp_ref.grad();
+    expect_rel(lp.val(), lp_ref.val(), std::fabs(lp_ref.val()), "beta value");
+    expect_vec(gy, adj(y), "beta d/dy");
+    for (int i = 0; i < n; ++i) {
+      const double dab = std::fabs(digamma(a_d[i] + b_d[i]));
+      expect_floor(ga[i], alpha[i].adj(), std::fabs(std::log(yb[i])) + dab + std::fabs(digamma(a_d[i])), "beta d/dalpha", i);
+      expect_floor(gb[i], beta[i].adj(), std::fabs(log1m(yb[i])) + dab + std::fabs(digamma(b_d[i])), "beta d/dbeta", i);
+    }
+    set_zero_all_adjoints();
+    STAN_CUDA_PARITY("beta propto, var y only", beta_lpdf<true>(y, a_d, b_d), beta_lpdf_reference_cpu<true>(y, a_d, b_d), adj(y));
+    const double v = beta_lpdf(yb, a_d, b_d);
+    expect_rel(v, beta_lpdf_reference_cpu<false>(yb, a_d, b_d), std::fabs(v), "beta, all double");
+    EXPECT_EQ(0.0, beta_lpdf<true>(yb, a_d, b_d));
+  }
+  {
+    vector_v y = to_v(d.y_pos), alpha = to_v(a_d), sigma = to_v(d.sigma);
+    var lp = weibull_lpdf(y, alpha, sigma);
+    lp.grad();
+    VectorXd gy = adj(y), ga = adj(alpha), gs = adj(sigma);
+    set_zero_all_adjoints();
+    var lp_ref = weibull_lpdf_reference_cpu<false>(y, alpha, sigma);
+    lp_ref.grad();
+    expect_rel(lp.val(), lp_ref.val(), std::fabs(lp_ref.val()), "weibull value");
+    for (int i = 0; i < n; ++i) {
+      const double pw = std::pow(d.y_pos[i] / d.sigma[i], a_d[i]);
+      expect_floor(gy[i], y[i].adj(), (std::fabs(a_d[i] - 1.0) + a_d[i] * pw) / d.y_pos[i], "weibull d/dy", i);
+      expect_floor(ga[i], alpha[i].adj(),
+                   1.0 / a_d[i] + (1.0 + pw) * (std::fabs(std::log(d.y_pos[i])) + std::fabs(std::log(d.sigma[i]))), "weibull d/dalpha", i);
+      expect_floor(gs[i], sigma[i].adj(), a_d[i] / d.sigma[i] * (pw + 1.0), "weibull d/dsigma", i);
+    }
+    set_zero_all_adjoints();
+    var s0 = 1.3;
+    {
+      var lq = weibull_lpdf<true>(d.y_pos, a_d, s0);
+      lq.grad();
+      const double g0 = s0.adj(), v0 = lq.val();
+      set_zero_all_adjoints();
+      var lq_ref = weibull_lpdf_reference_cpu<true>(d.y_pos, a_d, s0);
+      lq_ref.grad();
+      expect_rel(v0, lq_ref.val(), std::fabs(lq_ref.val()), "weibull propto, var scale: value");
+      double floor = 0;
+      for (int i = 0; i < n; ++i) floor += a_d[i] / 1.3 * (std::pow(d.y_pos[i] / 1.3, a_d[i]) + 1.0);
+      expect_floor(g0, s0.adj(), floor, "weibull propto, var scale: d/dsigma", 0);
+      set_zero_all_adjoints();
+    }
+    const double v = weibull_lpdf(d.y_pos, a_d, d.sigma);
+    expect_rel(v, weibull_lpdf_reference_cpu<false>(d.y_pos, a_d, d.sigma), std::fabs(v), "weibull, all double");
+    EXPECT_EQ(0.0, weibull_lpdf<true>(d.y_pos, a_d, d.sigma));
+  }
+  stan::math::recover_memory();
+}
+
 INSTANTIATE_TEST_CASE_P(Sizes, CudaLocScale, ::testing::Values(1, 3, 1000, 100003));
+
+TEST(CudaLocScaleErrors, beta_and_weibull_same_exceptions_and_log_zero_as_the_reference) {
+  using namespace stan::math;  // NOLINT
+  const int n = 2000;
+  Data d = make(n, 9);
+  VectorXd yb(n), a_d = d.sigma.array() + 0.2;
+  for (int i = 0; i < n; ++i) yb[i] = std::min(std::max(1.0 / (1.0 + std::exp(-d.y[i])), 1e-9), 1.0 - 1e-9);
+  vector_v alpha = to_v(a_d), second = to_v(d.sigma);
+  VectorXd yb_hi = yb, yb_nan = yb, yw_neg = d.y_pos, yw_inf = d.y_pos;
+  yb_hi[5] = 1.5;
+  yb_nan[5] = NAN;
+  yw_neg[5] = -0.5;
+  yw_inf[5] = INFINITY;
+  vector_v alpha_zero = to_v(a_d), second_inf = to_v(d.sigma);
+  alpha_zero[17] = 0.0;
+  second_inf[9] = INFINITY;
+  EXPECT_THROW(beta_lpdf(yb_hi, alpha, second), std::domain_error);
+  EXPECT_THROW(beta_lpdf(yb_nan, alpha, second), std::domain_error);
+  EXPECT_THROW(beta_lpdf(yb, alpha_zero, second), std::domain_error);
+  EXPECT_THROW(beta_lpdf(yb, alpha, second_inf), std::domain_error);
+  EXPECT_THROW(weibull_lpdf(yw_inf, alpha, second), std::domain_error);
+  EXPECT_THROW(weibull_lpdf(d.y_pos, alpha_zero, second), std::domain_error);
+  EXPECT_THROW(weibull_lpdf(d.y_pos, alpha, second_inf), std::domain_error);
+  vector_v shorter = to_v(d.sigma.head(n - 1));
+  EXPECT_THROW(beta_lpdf(yb, alpha, shorter), std::invalid_argument);
+  EXPECT_THROW(weibull_lpdf(d.y_pos, alpha, shorter), std::invalid_argument);
+  std::string m_gpu, m_cpu;
+  try {
+    beta_lpdf(yb_hi, alpha, second);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    beta_lpdf_reference_cpu<false>(yb_hi, alpha, second);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  m_gpu.clear();
+  m_cpu.clear();
+  try {
+    weibull_lpdf(d.y_pos, alpha, second_inf);
+  } catch (const std::domain_error& e) {
+    m_gpu = e.what();
+  }
+  try {
+    weibull_lpdf_reference_cpu<false>(d.y_pos, alpha, second_inf);
+  } catch (const std::domain_error& e) {
+    m_cpu = e.what();
+  }
+  EXPECT_EQ(m_gpu, m_cpu);
+  EXPECT_FALSE(m_gpu.empty());
+  EXPECT_EQ(LOG_ZERO, weibull_lpdf(yw_neg, alpha, second).val());                       // weibull_lpdf.hpp:56-61
+  EXPECT_EQ(LOG_ZERO, weibull_lpdf_reference_cpu<false>(yw_neg, alpha, second).val());
+  VectorXd none(0);
+  vector_v empty(0);
+  EXPECT_EQ(0.0, beta_lpdf(none, empty, empty).val());
+  EXPECT_EQ(0.0, weibull_lpdf(none, empty, empty).val());
+  stan::math::recover_memory();
+}
 
 TEST(CudaLocScaleErrors, gamma_and_exponential_same_exceptions_and_log_zero_as_the_reference) {
   using namespace stan::math;  // NOLINT

@@ -91,6 +91,8 @@ static_assert(std::is_same<decltype(stan::math::poisson_log_lpmf(ints(), vector_
 static_assert(std::is_same<decltype(stan::math::poisson_lpmf(ints(), vector_v())), var>::value, "");
 static_assert(std::is_same<decltype(stan::math::cauchy_lpdf(vector_d(), vector_v(), 1.0)), var>::value, "");
 static_assert(std::is_same<decltype(stan::math::gamma_lpdf(vector_d(), var(), vector_v())), var>::value, "");
+static_assert(std::is_same<decltype(stan::math::beta_lpdf(vector_v(), 2.0, 3.0)), var>::value, "");
+static_assert(std::is_same<decltype(stan::math::weibull_lpdf<true>(vector_d(), var(), vector_d())), var>::value, "");
 static_assert(std::is_same<decltype(stan::math::exponential_lpdf(vector_d(), vector_fd())), fvar<double>>::value, "");
 static_assert(std::is_same<decltype(stan::math::exponential_lpdf<true>(vector_v(), 1.5)), var>::value, "");
 static_assert(std::is_same<decltype(stan::math::lognormal_lpdf<true>(vector_d(), vector_d(), 1.0)), double>::value, "");

@@ -86,6 +86,29 @@ add("gamma_zero_outcome", "gamma", [0.0, 1.0, 2.0], [2.0, 0.5, 1.0], [1.0], var_
 add("exponential_scalar_beta", "exponential", yg[:n], [0.0], [1.3], var_mask=0b101)
 add("exponential_scalar_y", "exponential", [2.5], [0.0], be[:n], var_mask=0b101)
 
+# beta_lpdf(y | alpha, beta) and weibull_lpdf(y | alpha, sigma) (alpha in the mu slot): known answers of
+# test/prob/beta/beta_test.hpp:14-25 and test/prob/weibull/weibull_test.hpp:14-31, every subset of variables x propto,
+# scalar / vector operands, corners
+for i, (y, a, b, ka) in enumerate([(0.4, 0.5, 0.5, -0.4311717080293276382896), (0.5, 2.0, 5.0, -0.06453852113757105324332)]):
+    add("beta_ka%d" % i, "beta", [y], [a], [b], var_mask=0b111, known_answer=ka)
+for i, (y, a, sg, ka) in enumerate([(2.0, 1.0, 1.0, -2.0), (0.25, 2.9, 1.8, -3.277093769205283724233),
+                                    (3.9, 1.7, 0.25, -102.8962074392704266756)]):
+    add("weibull_ka%d" % i, "weibull", [y], [a], [sg], var_mask=0b111, known_answer=ka)
+yb = np.concatenate([rng.beta(2.0, 3.0, n), [1e-12, 1 - 1e-12, 0.5, 1e-3, 0.999, 0.25]])
+ab = np.concatenate([rng.uniform(0.3, 6.0, n), [0.01, 50.0, 1.0, 2.0, 300.0, 0.5]])
+bb = np.concatenate([rng.uniform(0.3, 6.0, n), [50.0, 0.01, 1.0, 0.5, 200.0, 2.0]])
+yw = np.concatenate([rng.weibull(1.5, n) * 2.0, [1e-8, 30.0, 1.0, 0.5, 1e-3, 5.0]])
+aw = np.concatenate([rng.uniform(0.4, 4.0, n), [0.1, 2.0, 1.0, 8.0, 0.5, 1.5]])
+sw = np.concatenate([rng.uniform(0.5, 3.0, n), [1.0, 10.0, 1.0, 0.6, 100.0, 2.0]])
+for density, yy, aa, ss in (("beta", yb, ab, bb), ("weibull", yw, aw, sw)):
+    for var_mask in range(8):
+        for propto in (False, True):
+            add("%s_vec_m%d%s" % (density, var_mask, "_propto" if propto else ""), density, yy, aa, ss, propto=propto,
+                var_mask=var_mask)
+    add(density + "_scalar_shapes", density, yy[:n], [1.7], [2.3], var_mask=0b111)
+    add(density + "_scalar_y", density, [0.3], aa[:n], ss[:n], var_mask=0b111)
+    add(density + "_scalar_second", density, yy[:n], aa[:n], [0.8], var_mask=0b110)
+
 out["cases"] = np.array(names)
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "locscale_golden.npz")
 np.savez_compressed(path, **out)

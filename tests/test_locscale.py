@@ -49,12 +49,45 @@ def check_gamma_dalpha(got, ref, c, what, rtol):
     assert not (err > rtol).any(), "%s dmu: %d components off, worst %.3e" % (what, int((err > rtol).sum()), err.max())
 
 
+def check_beta_shape_partial(got, ref, c, key, what, rtol):
+    """d/dalpha = log(y) + digamma(alpha + beta) - digamma(alpha), d/dbeta = log1m(y) + ... (beta_lpdf.hpp:170-177)"""
+    from scipy.special import digamma
+    y, a, b = (np.asarray(c[k], float) for k in ("y", "mu", "sigma"))
+    own = a if key == "dmu" else b
+    terms = np.abs(np.log(y) if key == "dmu" else np.log1p(-y)) + np.abs(digamma(a + b)) + np.abs(digamma(own))
+    terms = np.broadcast_to(terms, (max(y.size, a.size, b.size),))
+    scale = np.maximum(np.abs(ref), terms if ref.size > 1 else terms.sum())
+    err = np.abs(np.asarray(got, float) - ref) / scale
+    assert not (err > rtol).any(), "%s %s: %d components off, worst %.3e" % (what, key, int((err > rtol).sum()), err.max())
+
+
+def weibull_scale(c, key, size):
+    """weibull's partials are products / sums of (y / sigma)^alpha, logs and reciprocals (weibull_lpdf.hpp:125-139): the
+    floor is the magnitude of their terms"""
+    y, a, s = (np.asarray(c[k], float) for k in ("y", "mu", "sigma"))
+    pw = np.power(y / s, a)
+    if key == "dy":
+        terms = (np.abs(a - 1.0) + a * pw) / y
+    elif key == "dmu":
+        terms = 1.0 / a + (1.0 + pw) * (np.abs(np.log(y)) + np.abs(np.log(s)))
+    else:
+        terms = a / s * (pw + 1.0)
+    terms = np.broadcast_to(terms, (max(y.size, a.size, s.size),))
+    return terms if size > 1 else np.array([terms.sum()])
+
+
 def check_case(r, c, what, rtol=1e-10):
     assert r["rc"] == 0, what
     assert_close(r["lp"], c["lp"], what + " lp", rtol)
     for k, bit in KEYS:
         if c["var_mask"] & bit and k == "dmu" and c.get("density") == _abi.LOCSCALE_GAMMA:
             check_gamma_dalpha(r[k], np.asarray(c[k], float), c, what, rtol)
+        elif c["var_mask"] & bit and k != "dy" and c.get("density") == _abi.LOCSCALE_BETA:
+            check_beta_shape_partial(r[k], np.asarray(c[k], float), c, k, what, rtol)
+        elif c["var_mask"] & bit and c.get("density") == _abi.LOCSCALE_WEIBULL:
+            ref = np.asarray(c[k], float)
+            err = np.abs(np.asarray(r[k], float) - ref) / np.maximum(np.abs(ref), weibull_scale(c, k, ref.size))
+            assert not (err > rtol).any(), "%s %s: %d components off, worst %.3e" % (what, k, int((err > rtol).sum()), err.max())
         elif c["var_mask"] & bit:
             assert_close(r[k], c[k], what + " " + k, rtol)
             # element by element: relative to the element, floored at 1e-8 of the largest one
@@ -68,7 +101,7 @@ def check_case(r, c, what, rtol=1e-10):
 def test_oracle_matches_golden_and_known_answers(golden_ls):
     """outputs of the compiled reference and the literal expected values of test/prob/cauchy/cauchy_test.hpp:10-31,
     test/prob/lognormal/lognormal_test.hpp:10-25"""
-    assert len(golden_ls["cases"]) >= 81
+    assert len(golden_ls["cases"]) >= 124
     known = 0
     for name in golden_ls["cases"]:
         c = ls_case(golden_ls, str(name))
@@ -77,7 +110,7 @@ def test_oracle_matches_golden_and_known_answers(golden_ls):
         if "known_answer" in c:
             known += 1
             assert abs(r["lp"] - c["known_answer"]) <= 1e-13 * max(1.0, abs(c["known_answer"])), name
-    assert known == 11   # 3 cauchy, 2 lognormal, 3 gamma, 3 exponential
+    assert known == 16   # 3 cauchy, 2 lognormal, 3 gamma, 3 exponential, 2 beta, 3 weibull
 
 
 def test_oracle_codes():
@@ -97,6 +130,15 @@ def test_oracle_codes():
     assert L.oracle_locscale_lpdf("gamma", [np.nan], [1.0], [1.0])["rc"] == _abi.BAD_OPERAND
     r = L.oracle_locscale_lpdf("gamma", [1.0, -0.5], [1.0], [1.0])
     assert r["rc"] == _abi.LOG_ZERO and r["lp"] == -np.inf                                  # gamma_lpdf.hpp:69-74
+    for bad in (0.0, -1.0, np.inf, -np.inf, np.nan):     # test/prob/beta/beta_test.hpp:36-60, weibull_test.hpp:37-49
+        for d in ("beta", "weibull"):
+            assert L.oracle_locscale_lpdf(d, [0.5], [bad], [1.0])["rc"] == _abi.BAD_OPERAND
+            assert L.oracle_locscale_lpdf(d, [0.5], [1.0], [bad])["rc"] == _abi.BAD_OPERAND
+    for bad_y in (-1.0, 2.0, np.nan):
+        assert L.oracle_locscale_lpdf("beta", [bad_y], [1.0], [1.0])["rc"] == _abi.BAD_OPERAND
+    for bad_y in (np.inf, np.nan):
+        assert L.oracle_locscale_lpdf("weibull", [bad_y], [1.0], [1.0])["rc"] == _abi.BAD_OPERAND
+    assert L.oracle_locscale_lpdf("weibull", [1.0, -0.5], [1.0], [1.0])["rc"] == _abi.LOG_ZERO   # weibull_lpdf.hpp:56-61
     for bad_y in (-10.0, np.nan):                       # test/prob/exponential/exponential_test.hpp:31-36
         assert L.oracle_locscale_lpdf("exponential", [bad_y], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
     assert L.oracle_locscale_lpdf("lognormal", [-1.0], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
@@ -115,6 +157,10 @@ def synth(density, n, rng):
     elif density in ("gamma", "exponential"):
         y = rng.gamma(2.0, 1.5, n)
         mu = rng.uniform(0.2, 8.0, n) if density == "gamma" else np.zeros(1)
+    elif density == "beta":
+        y, mu, sg = rng.beta(2.0, 3.0, n).clip(1e-9, 1 - 1e-9), rng.uniform(0.3, 6.0, n), rng.uniform(0.3, 6.0, n)
+    elif density == "weibull":
+        y, mu = rng.weibull(1.5, n) * 2.0 + 1e-6, rng.uniform(0.4, 4.0, n)
     return y, mu, sg
 
 
@@ -122,7 +168,7 @@ def masks(density):
     return (0, 1, 4, 5) if density == "exponential" else range(8)
 
 
-DENSITIES = ["normal", "cauchy", "lognormal", "gamma", "exponential"]
+DENSITIES = ["normal", "cauchy", "lognormal", "gamma", "exponential", "beta", "weibull"]
 
 
 @needs_ref
@@ -142,6 +188,11 @@ def test_oracle_vs_compiled_reference(density):
                 for k, bit in KEYS:
                     if var_mask & bit and k == "dmu" and density == "gamma":
                         check_gamma_dalpha(got[k], ref[k], c, "gamma", 1e-12)
+                    elif var_mask & bit and k != "dy" and density == "beta":
+                        check_beta_shape_partial(got[k], ref[k], c, k, "beta", 1e-12)
+                    elif var_mask & bit and density == "weibull":
+                        err = np.abs(got[k] - ref[k]) / np.maximum(np.abs(ref[k]), weibull_scale(c, k, ref[k].size))
+                        assert not (err > 1e-12).any(), ("weibull", k, err.max())
                     elif var_mask & bit:   # (a scalar operand's partial is a sum of n terms that may cancel: the parity bar)
                         assert_close(got[k], ref[k], "%s %s" % (density, k), 1e-12 if np.size(ref[k]) > 1 else 1e-10)
 
@@ -283,3 +334,45 @@ def test_device_gamma_and_exponential_wrappers(glm, golden_ls):
     assert not isinstance(e.value, glm.DomainError)
     assert glm.gamma_lpdf([], [], [])[0] == 0.0 and glm.exponential_lpdf([], [])[0] == 0.0
     assert glm.gamma_lpdf(y, al, be, propto=True, var_mask=0)[0] == 0.0
+
+
+@pytest.mark.gpu
+def test_device_beta_and_weibull_wrappers(glm, golden_ls):
+    """glm.beta_lpdf / glm.weibull_lpdf against the golden vectors (value), and their error contract
+    (beta_lpdf.hpp:48-56, weibull_lpdf.hpp:38-61; the invalid values of the reference's fixtures)"""
+    for name in golden_ls["cases"]:
+        c = ls_case(golden_ls, str(name))
+        f = {_abi.LOCSCALE_BETA: glm.beta_lpdf, _abi.LOCSCALE_WEIBULL: glm.weibull_lpdf}.get(c["density"])
+        if f is None:
+            continue
+        lp, g = f(c["y"], c["mu"], c["sigma"], propto=c["propto"], var_mask=c["var_mask"])
+        assert_close(lp, c["lp"], "wrapper vs golden %s lp" % name)
+        assert sorted(g) == sorted(nm for nm, bit in (("y", 1), ("alpha", 2), ("beta" if f is glm.beta_lpdf else "sigma", 4))
+                                   if c["var_mask"] & bit)
+    n = 3000
+    y, a, b = np.linspace(0.05, 0.95, n), np.linspace(0.5, 4, n), np.linspace(0.5, 2, n)
+    for f, d in ((glm.beta_lpdf, "beta"), (glm.weibull_lpdf, "weibull")):
+        for bad_value in (0.0, -1.0, np.inf, np.nan):
+            for k in (1, 2):
+                ops = [y.copy(), a.copy(), b.copy()]
+                ops[k][1234] = bad_value
+                with pytest.raises(glm.DomainError):
+                    f(*ops)
+                assert glm.locscale_eval(d, *ops, glm.locscale_flags(d), y_is_data=False)["rc"] == _abi.BAD_OPERAND
+        with pytest.raises(ValueError) as e:
+            f(y[:10], a[:9], b[:10])
+        assert not isinstance(e.value, glm.DomainError)
+        assert f([], [], [])[0] == 0.0 and f(y, a, b, propto=True, var_mask=0)[0] == 0.0
+    for bad_y in (-0.1, 1.5, np.nan):
+        yy = y.copy()
+        yy[9] = bad_y
+        with pytest.raises(glm.DomainError):
+            glm.beta_lpdf(yy, a, b)
+        assert glm.locscale_eval("beta", yy, a, b, glm.locscale_flags("beta"), y_is_data=False)["rc"] == _abi.BAD_OPERAND
+    yy = y.copy()
+    yy[9] = -0.5
+    lp, g = glm.weibull_lpdf(yy, a, b)          # a negative outcome: LOG_ZERO, no partials
+    assert lp == -np.inf and g == {}
+    yy[9] = np.inf
+    with pytest.raises(glm.DomainError):
+        glm.weibull_lpdf(yy, a, b)
