@@ -201,6 +201,10 @@ typedef struct stan_cuda_normal_args {
  *     LP_Y = (alpha - 1) * log(y), LP_SCALE = -alpha * log(sigma), LP_MAIN = -(y / sigma)^alpha. */
 #define STAN_CUDA_LOCSCALE_BETA 5        /* prim/scal/prob/beta_lpdf.hpp:40-181 */
 #define STAN_CUDA_LOCSCALE_WEIBULL 6     /* prim/scal/prob/weibull_lpdf.hpp:29-143 */
+/*   inv_gamma_lpdf(y | alpha, beta): the slots and flags of gamma_lpdf.  Summands (inv_gamma_lpdf.hpp:115-126):
+ *     LP_DOF = -lgamma(alpha), LP_SCALE = alpha * log(beta), LP_Y = -(alpha + 1) * log(y), LP_MAIN = -beta / y;
+ *     LOG_ZERO for an outcome that is not positive (:58-63). */
+#define STAN_CUDA_LOCSCALE_INV_GAMMA 7   /* prim/scal/prob/inv_gamma_lpdf.hpp:33-146 */
 /* lognormal only: the -sum log(y) term, which the reference ties to include_summand<propto, T_y>
  * (lognormal_lpdf.hpp:113-115) */
 #define STAN_CUDA_LP_Y 0x1000u

@@ -116,9 +116,10 @@ class MultiplyArgs(C.Structure):
     ]
 
 
-LOCSCALE_NORMAL, LOCSCALE_CAUCHY, LOCSCALE_LOGNORMAL, LOCSCALE_GAMMA, LOCSCALE_EXPONENTIAL, LOCSCALE_BETA, LOCSCALE_WEIBULL = range(7)
+(LOCSCALE_NORMAL, LOCSCALE_CAUCHY, LOCSCALE_LOGNORMAL, LOCSCALE_GAMMA, LOCSCALE_EXPONENTIAL, LOCSCALE_BETA, LOCSCALE_WEIBULL,
+ LOCSCALE_INV_GAMMA) = range(8)
 LOCSCALES = {"normal": LOCSCALE_NORMAL, "cauchy": LOCSCALE_CAUCHY, "lognormal": LOCSCALE_LOGNORMAL, "gamma": LOCSCALE_GAMMA,
-             "exponential": LOCSCALE_EXPONENTIAL, "beta": LOCSCALE_BETA, "weibull": LOCSCALE_WEIBULL}
+             "exponential": LOCSCALE_EXPONENTIAL, "beta": LOCSCALE_BETA, "weibull": LOCSCALE_WEIBULL, "inv_gamma": LOCSCALE_INV_GAMMA}
 LP_Y = 0x1000
 DENSITY_BERNOULLI_LOGIT, DENSITY_POISSON_LOG, DENSITY_POISSON, DENSITY_BERNOULLI = 1, 2, 3, 4
 DENSITIES = {"bernoulli_logit": DENSITY_BERNOULLI_LOGIT, "poisson_log": DENSITY_POISSON_LOG, "poisson": DENSITY_POISSON,

@@ -876,7 +876,7 @@ int normal_lpdf_eval(const stan_cuda_normal_args* a) { return locscale_lpdf_eval
 int locscale_lpdf_eval(int family, const stan_cuda_normal_args* a) {
   NvtxRange range("stan_cuda_locscale_lpdf_eval");
   if (!a) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: null args");
-  if (family < STAN_CUDA_LOCSCALE_NORMAL || family > STAN_CUDA_LOCSCALE_WEIBULL)
+  if (family < STAN_CUDA_LOCSCALE_NORMAL || family > STAN_CUDA_LOCSCALE_INV_GAMMA)
     return fail(STAN_CUDA_ERR_ARG, "stan_cuda_locscale_lpdf_eval: unknown density");
   if (a->n < 0) return fail(STAN_CUDA_ERR_ARG, "stan_cuda_normal_lpdf_eval: negative n");
   if (a->n == 0) {  // size_zero(y, mu, sigma) -> 0 (normal_lpdf.hpp:45-47)

@@ -23,6 +23,7 @@ struct NormalKernelParams {
 //   exponential_lpdf stan/math/prim/scal/prob/exponential_lpdf.hpp:55-90  (beta in the sigma slot, mu unused)
 //   beta_lpdf       stan/math/prim/scal/prob/beta_lpdf.hpp:48-177         (alpha in the mu slot, beta in the sigma slot)
 //   weibull_lpdf    stan/math/prim/scal/prob/weibull_lpdf.hpp:38-139      (alpha in the mu slot)
+//   inv_gamma_lpdf  stan/math/prim/scal/prob/inv_gamma_lpdf.hpp:58-140    (the slots of gamma_lpdf)
 template <int FAMILY, int THREADS>
 __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernelParams p) {
   const NormalIO& io = p.io;
@@ -47,7 +48,8 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
       if (lp_scale) log_sigma = log(sg);
     }
     bad |= isnan(y) ? 1u : 0u;
-    if (FAMILY == STAN_CUDA_LOCSCALE_GAMMA || FAMILY == STAN_CUDA_LOCSCALE_BETA || FAMILY == STAN_CUDA_LOCSCALE_WEIBULL)
+    if (FAMILY == STAN_CUDA_LOCSCALE_GAMMA || FAMILY == STAN_CUDA_LOCSCALE_BETA || FAMILY == STAN_CUDA_LOCSCALE_WEIBULL ||
+        FAMILY == STAN_CUDA_LOCSCALE_INV_GAMMA)
       bad |= (mu > 0.0 && isfinite(mu)) ? 0u : 2u;  // the shape: positive and finite
     else if (FAMILY != STAN_CUDA_LOCSCALE_EXPONENTIAL) bad |= isfinite(mu) ? 0u : 2u;
     if (io.sigma_vec) bad |= (sg > 0.0 && (FAMILY == STAN_CUDA_LOCSCALE_NORMAL || isfinite(sg))) ? 0u : 4u;
@@ -84,6 +86,18 @@ __global__ void __launch_bounds__(THREADS) normal_lpdf_kernel(const NormalKernel
       d_y = (mu - 1.0) / y - sg;                                         // :131-133
       d_mu = (io.flags & STAN_CUDA_NEED_DALPHA) ? -digamma_pos(mu) + log_beta + log_y : 0.0;  // :134-137
       d_sigma = mu / sg - y;                                             // :138-140
+    } else if (FAMILY == STAN_CUDA_LOCSCALE_INV_GAMMA) {
+      // inv_gamma_lpdf.hpp:58-140 with alpha = mu, beta = sg
+      bad |= (y <= 0.0) ? 8u : 0u;                     // :58-63 LOG_ZERO
+      const double log_y = y > 0.0 ? log(y) : 0.0, inv_y = 1.0 / y;      // :76-86
+      const double log_beta = log(sg);                 // :106-110
+      if (io.flags & STAN_CUDA_LP_DOF) lp -= lgamma(mu);               // :115-117
+      if (lp_scale) lp += mu * log_beta;                                 // :118-120
+      if (lp_y) lp -= (mu + 1.0) * log_y;                                // :121-123
+      if (lp_main) lp -= sg * inv_y;                                     // :124-126
+      d_y = -(mu + 1.0) * inv_y + sg * inv_y * inv_y;                    // :128-131
+      d_mu = (io.flags & STAN_CUDA_NEED_DALPHA) ? -digamma_pos(mu) + log_beta - log_y : 0.0;  // :132-135
+      d_sigma = mu / sg - inv_y;                                         // :136-138
     } else if (FAMILY == STAN_CUDA_LOCSCALE_BETA) {
       // beta_lpdf.hpp:48-176 with alpha = mu, beta = sg; five summands, a flag each (include/stan_cuda.h)
       bad |= (y < 0.0 || y > 1.0) ? 1u : 0u;           // :53-54 check_nonnegative / check_less_or_equal(y, 1)
@@ -225,6 +239,9 @@ int launch_normal_lpdf(const NormalIO& io, Workspace* ws, int device, cudaStream
       break;
     case STAN_CUDA_LOCSCALE_WEIBULL:
       normal_lpdf_kernel<STAN_CUDA_LOCSCALE_WEIBULL, THREADS><<<grid, THREADS, 0, stream>>>(p);
+      break;
+    case STAN_CUDA_LOCSCALE_INV_GAMMA:
+      normal_lpdf_kernel<STAN_CUDA_LOCSCALE_INV_GAMMA, THREADS><<<grid, THREADS, 0, stream>>>(p);
       break;
     default:
       return fail(STAN_CUDA_ERR_ARG, "launch_normal_lpdf: unknown density");

@@ -497,7 +497,7 @@ def locscale_flags(density, propto=False, var_mask=0b110):
     d = _abi.LOCSCALES[density] if isinstance(density, str) else density
     vy, vm, vs = bool(var_mask & 1), bool(var_mask & 2), bool(var_mask & 4)
     f = (_abi.NEED_DY if vy else 0) | (_abi.NEED_DALPHA if vm else 0) | (_abi.NEED_DSIGMA if vs else 0)
-    if d == _abi.LOCSCALE_GAMMA:        # gamma_lpdf.hpp:118-129 (alpha = the mu operand, beta = the sigma operand)
+    if d in (_abi.LOCSCALE_GAMMA, _abi.LOCSCALE_INV_GAMMA):   # gamma_lpdf.hpp:118-129, inv_gamma_lpdf.hpp:115-126 (alpha = mu, beta = sigma)
         f |= (_abi.LP_DOF if (not propto or vm) else 0) | (_abi.LP_SCALE if (not propto or vm or vs) else 0)
         f |= (_abi.LP_Y if (not propto or vy or vm) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
         return f
@@ -604,6 +604,17 @@ def weibull_lpdf(y, alpha, sigma, propto=False, var_mask=0b110, y_is_data=True):
             raise DomainError("weibull_lpdf: Random variable must be finite")
     return _shape_density("weibull_lpdf", "weibull", y, alpha, sigma, propto, var_mask, y_is_data, y_check, "Scale parameter",
                           (("y", "dy", 1), ("alpha", "dmu", 2), ("sigma", "dsigma", 4)))
+
+
+def inv_gamma_lpdf(y, alpha, beta, propto=False, var_mask=0b110, y_is_data=True):
+    """stan/math/prim/scal/prob/inv_gamma_lpdf.hpp:33-35; var_mask: which of y (bit 0), alpha (1), beta (2) are variables;
+    an outcome that is not positive is LOG_ZERO (:58-63)."""
+    def y_check(y):
+        if np.any(np.isnan(y)):
+            raise DomainError("inv_gamma_lpdf: Random variable is nan")
+    # (the reference tests y first, :41-43; with the operands all valid or one invalid the order is not observable here)
+    return _shape_density("inv_gamma_lpdf", "inv_gamma", y, alpha, beta, propto, var_mask, y_is_data, y_check, "Scale parameter",
+                          (("y", "dy", 1), ("alpha", "dmu", 2), ("beta", "dsigma", 4)))
 
 
 def exponential_lpdf(y, beta, propto=False, var_mask=0b10, y_is_data=True):

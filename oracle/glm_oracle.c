@@ -472,12 +472,49 @@ static int oracle_beta_weibull(int density, const stan_cuda_normal_args* a) {
   return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
 }
 
+/* inv_gamma_lpdf(y | alpha, beta), stan/math/prim/scal/prob/inv_gamma_lpdf.hpp:33-146; alpha in the mu slot, beta in the
+ * sigma slot */
+static int oracle_inv_gamma(const stan_cuda_normal_args* a) {
+  for (int64_t i = 0; i < a->y_len; ++i) if (isnan(a->y[i])) return STAN_CUDA_BAD_OPERAND;                 /* :41 */
+  for (int64_t i = 0; i < a->mu_len; ++i)
+    if (!(a->mu[i] > 0.0) || !isfinite(a->mu[i])) return STAN_CUDA_BAD_OPERAND;                           /* :42 */
+  for (int64_t i = 0; i < a->sigma_len; ++i)
+    if (!(a->sigma[i] > 0.0) || !isfinite(a->sigma[i])) return STAN_CUDA_BAD_OPERAND;                     /* :43 */
+  for (int64_t i = 0; i < a->y_len; ++i)
+    if (a->y[i] <= 0) {                                                                                   /* :58-63 */
+      if (a->lp) *a->lp = -INFINITY;
+      return STAN_CUDA_LOG_ZERO;
+    }
+  const int ym = a->y_len != 1, mm = a->mu_len != 1, sm = a->sigma_len != 1;
+  const int need_mu = (a->flags & STAN_CUDA_NEED_DALPHA) && a->dmu;
+  const int need_sigma = (a->flags & STAN_CUDA_NEED_DSIGMA) && a->dsigma;
+  const int need_y = (a->flags & STAN_CUDA_NEED_DY) && a->dy;
+  if (need_mu) for (int64_t i = 0; i < a->mu_len; ++i) a->dmu[i] = 0.0;
+  if (need_sigma) for (int64_t i = 0; i < a->sigma_len; ++i) a->dsigma[i] = 0.0;
+  if (need_y) for (int64_t i = 0; i < a->y_len; ++i) a->dy[i] = 0.0;
+  double logp = 0.0;
+  for (int64_t n = 0; n < a->n; ++n) {
+    const double y = a->y[ym ? n : 0], alpha = a->mu[mm ? n : 0], beta = a->sigma[sm ? n : 0];
+    const double log_y = log(y), inv_y = 1.0 / y, log_beta = log(beta);                      /* :76-110 */
+    if (a->flags & STAN_CUDA_LP_DOF) logp -= lgamma(alpha);                                 /* :115-117 */
+    if (a->flags & STAN_CUDA_LP_SCALE) logp += alpha * log_beta;                            /* :118-120 */
+    if (a->flags & STAN_CUDA_LP_Y) logp -= (alpha + 1.0) * log_y;                           /* :121-123 */
+    if (a->flags & STAN_CUDA_LP_MAIN) logp -= beta * inv_y;                                 /* :124-126 */
+    if (need_y) a->dy[ym ? n : 0] += -(alpha + 1) * inv_y + beta * inv_y * inv_y;           /* :128-131 */
+    if (need_mu) a->dmu[mm ? n : 0] += -oracle_digamma(alpha) + log_beta - log_y;           /* :132-135 */
+    if (need_sigma) a->dsigma[sm ? n : 0] += alpha / beta - inv_y;                          /* :136-138 */
+  }
+  if (a->lp) *a->lp = logp;
+  return isfinite(logp) ? STAN_CUDA_OK : STAN_CUDA_NONFINITE;
+}
+
 int oracle_locscale_lpdf_eval(int density, const stan_cuda_normal_args* a) {
-  if (!a || a->n < 0 || density < STAN_CUDA_LOCSCALE_NORMAL || density > STAN_CUDA_LOCSCALE_WEIBULL) return STAN_CUDA_ERR_ARG;
+  if (!a || a->n < 0 || density < STAN_CUDA_LOCSCALE_NORMAL || density > STAN_CUDA_LOCSCALE_INV_GAMMA) return STAN_CUDA_ERR_ARG;
   if (a->n == 0) {
     if (a->lp) *a->lp = 0.0;
     return STAN_CUDA_OK;
   }
+  if (density == STAN_CUDA_LOCSCALE_INV_GAMMA) return oracle_inv_gamma(a);
   if (density >= STAN_CUDA_LOCSCALE_BETA) return oracle_beta_weibull(density, a);
   if (density >= STAN_CUDA_LOCSCALE_GAMMA) return oracle_gamma_exponential(density, a);
   const int lognormal = density == STAN_CUDA_LOCSCALE_LOGNORMAL, normal = density == STAN_CUDA_LOCSCALE_NORMAL;

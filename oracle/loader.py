@@ -389,7 +389,7 @@ def locscale_flags(density, propto=False, var_mask=0b110):
     d = _abi.LOCSCALES[density] if isinstance(density, str) else density
     vy, vm, vs = bool(var_mask & 1), bool(var_mask & 2), bool(var_mask & 4)
     f = (_abi.NEED_DY if vy else 0) | (_abi.NEED_DALPHA if vm else 0) | (_abi.NEED_DSIGMA if vs else 0)
-    if d == _abi.LOCSCALE_GAMMA:        # gamma_lpdf.hpp:118-129 (alpha = the mu operand, beta = the sigma operand)
+    if d in (_abi.LOCSCALE_GAMMA, _abi.LOCSCALE_INV_GAMMA):   # gamma_lpdf.hpp:118-129, inv_gamma_lpdf.hpp:115-126 (alpha = mu, beta = sigma)
         f |= (_abi.LP_DOF if (not propto or vm) else 0) | (_abi.LP_SCALE if (not propto or vm or vs) else 0)
         f |= (_abi.LP_Y if (not propto or vy or vm) else 0) | (_abi.LP_MAIN if (not propto or vy or vs) else 0)
         return f

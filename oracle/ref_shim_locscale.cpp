@@ -109,6 +109,14 @@ struct Call<6, propto> {  // weibull_lpdf(y | alpha, sigma)
   }
 };
 
+template <bool propto>
+struct Call<7, propto> {  // inv_gamma_lpdf(y | alpha, beta)
+  template <typename A, typename B, typename C>
+  static auto go(const A& y, const B& alpha, const C& beta) -> decltype(stan::math::inv_gamma_lpdf<propto>(y, alpha, beta)) {
+    return stan::math::inv_gamma_lpdf<propto>(y, alpha, beta);
+  }
+};
+
 // peel one operand at a time into its static type, then call the reference
 template <int FAMILY, bool propto, typename... Done>
 struct Dispatch {
@@ -139,7 +147,7 @@ extern "C" {
 
 // density 0: normal_lpdf, 1: cauchy_lpdf, 2: lognormal_lpdf, 3: gamma_lpdf(y | alpha = mu, beta = sigma),
 // 4: exponential_lpdf(y | beta = sigma; pass mu as one double), 5: beta_lpdf(y | alpha = mu, beta = sigma),
-// 6: weibull_lpdf(y | alpha = mu, sigma).  var_mask bit 0: y, bit 1: mu, bit 2: sigma.  Lengths are 1
+// 6: weibull_lpdf(y | alpha = mu, sigma), 7: inv_gamma_lpdf(y | alpha = mu, beta = sigma).  var_mask bit 0: y, bit 1: mu, bit 2: sigma.  Lengths are 1
 // (scalar) or n (vector).  Returns 0, or 1 (std::domain_error) / 2 (std::invalid_argument) / 3 (other) with the
 // exception text in err.
 int stanref_locscale_lpdf(int density, int propto, int var_mask, const double* y, long y_len, const double* mu, long mu_len,
@@ -155,7 +163,8 @@ int stanref_locscale_lpdf(int density, int propto, int var_mask, const double* y
                      : density == 2 ? run_family<2>(propto != 0, oy, om, os)
                      : density == 3 ? run_family<3>(propto != 0, oy, om, os)
                      : density == 4 ? run_family<4>(propto != 0, oy, om, os)
-                     : density == 5 ? run_family<5>(propto != 0, oy, om, os) : run_family<6>(propto != 0, oy, om, os);
+                     : density == 5 ? run_family<5>(propto != 0, oy, om, os)
+                     : density == 6 ? run_family<6>(propto != 0, oy, om, os) : run_family<7>(propto != 0, oy, om, os);
     auto t1 = std::chrono::steady_clock::now();
     if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
     if (lp) *lp = r;

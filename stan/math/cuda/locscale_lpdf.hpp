@@ -15,7 +15,7 @@ namespace math {
 namespace cuda {
 
 /**
- * cauchy_lpdf, lognormal_lpdf, gamma_lpdf, exponential_lpdf, beta_lpdf and weibull_lpdf on the device: the operands, their staging and the tape node are
+ * cauchy_lpdf, lognormal_lpdf, gamma_lpdf, exponential_lpdf, beta_lpdf, weibull_lpdf and inv_gamma_lpdf on the device: the operands, their staging and the tape node are
  * those of normal_lpdf_device (stan/math/cuda/normal_lpdf.hpp); the density id selects the per-element term of the
  * kernel (stan_cuda_locscale_lpdf_eval).  Eligible calls: the vectorised ones with something to compute -- when
  * include_summand<propto, T_y, T_loc, T_scale> is false the reference body only runs its checks, and stays in charge.
@@ -113,6 +113,21 @@ struct weibull_checks {
   template <typename T_y, typename T_a, typename T_s>
   static void sizes(const T_y& y, const T_a& alpha, const T_s& sigma) {
     check_consistent_sizes(function(), "Random variable", y, "Shape parameter", alpha, "Scale parameter", sigma);
+  }
+};
+
+/** the eager checks of inv_gamma_lpdf.hpp:41-43 */
+struct inv_gamma_checks {
+  static const char* function() { return "inv_gamma_lpdf"; }
+  template <typename T_y, typename T_a, typename T_b>
+  static void run(const T_y& y, const T_a& alpha, const T_b& beta) {
+    check_not_nan(function(), "Random variable", y);
+    check_positive_finite(function(), "Shape parameter", alpha);
+    check_positive_finite(function(), "Scale parameter", beta);
+  }
+  template <typename T_y, typename T_a, typename T_b>
+  static void sizes(const T_y& y, const T_a& alpha, const T_b& beta) {
+    check_consistent_sizes(function(), "Random variable", y, "Shape parameter", alpha, "Scale parameter", beta);
   }
 };
 
@@ -289,6 +304,25 @@ return_type_t<T_y, T_shape, T_scale> weibull_lpdf_device(const T_y& y, const T_s
                             | (include_summand<propto, T_y, T_shape>::value ? STAN_CUDA_LP_Y : 0u)
                             | (include_summand<propto, T_shape, T_scale>::value ? STAN_CUDA_LP_SCALE : 0u) | STAN_CUDA_LP_MAIN;
   return detail::locscale_lpdf_call<detail::weibull_checks>(STAN_CUDA_LOCSCALE_WEIBULL, summands, y, alpha, sigma);
+}
+
+/**
+ * GPU body of the vectorised inv_gamma_lpdf (reference: stan/math/prim/scal/prob/inv_gamma_lpdf.hpp:33-146): gamma_lpdf's
+ * slots and flags with the terms of :115-138 and LOG_ZERO for an outcome that is not positive (:58-63).  Checks before
+ * sizes, as there (:41-48).
+ */
+template <bool propto, typename T_y, typename T_shape, typename T_scale>
+return_type_t<T_y, T_shape, T_scale> inv_gamma_lpdf_device(const T_y& y, const T_shape& alpha, const T_scale& beta) {
+  if (size_zero(y, alpha, beta)) {
+    detail::inv_gamma_checks::run(y, alpha, beta);
+    detail::inv_gamma_checks::sizes(y, alpha, beta);
+    return 0.0;
+  }
+  const uint32_t summands = (include_summand<propto, T_shape>::value ? STAN_CUDA_LP_DOF : 0u)
+                            | (include_summand<propto, T_shape, T_scale>::value ? STAN_CUDA_LP_SCALE : 0u)
+                            | (include_summand<propto, T_y, T_shape>::value ? STAN_CUDA_LP_Y : 0u)
+                            | (include_summand<propto, T_y, T_scale>::value ? STAN_CUDA_LP_MAIN : 0u);
+  return detail::locscale_lpdf_call<detail::inv_gamma_checks>(STAN_CUDA_LOCSCALE_INV_GAMMA, summands, y, alpha, beta);
 }
 
 }  // namespace cuda

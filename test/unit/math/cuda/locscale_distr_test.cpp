@@ -16,6 +16,7 @@
 #include <test/prob/exponential/exponential_test.hpp>
 #include <test/prob/beta/beta_test.hpp>
 #include <test/prob/weibull/weibull_test.hpp>
+#include <test/prob/inv_gamma/inv_gamma_test.hpp>
 #include <vector>
 
 typedef Eigen::Matrix<var, Eigen::Dynamic, 1> vector_var;
@@ -77,6 +78,15 @@ STAN_CUDA_DISTR(AgradDistributionsWeibull, 4)
 STAN_CUDA_DISTR(AgradDistributionsWeibull, 5)
 STAN_CUDA_DISTR(AgradDistributionsWeibull, 6)
 STAN_CUDA_DISTR(AgradDistributionsWeibull, 7)
+
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 0)
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 1)
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 2)
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 3)
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 4)
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 5)
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 6)
+STAN_CUDA_DISTR(AgradDistributionsInvGamma, 7)
 
 // exponential_lpdf(y | beta): two operands
 typedef boost::mpl::vector<std::vector<double>, var, empty, empty, empty, empty> type_e_0;   // data y, var rate: the model statement

@@ -169,6 +169,45 @@ TEST_P(CudaLocScale, gamma_and_exponential_match_reference_loop) {
   stan::math::recover_memory();
 }
 
+TEST_P(CudaLocScale, inv_gamma_matches_reference_loop) {
+  const int n = GetParam();
+  Data d = make(n, 500 + n);
+  VectorXd al_d = d.sigma.array() + 0.2;
+  vector_v y = to_v(d.y_pos), alpha = to_v(al_d), beta = to_v(d.sigma);
+  var alpha0 = 2.2, beta0 = 1.3;
+  using namespace stan::math;  // NOLINT
+  STAN_CUDA_PARITY("inv_gamma, var y and beta vectors", inv_gamma_lpdf(y, al_d, beta), inv_gamma_lpdf_reference_cpu<false>(y, al_d, beta),
+                   adj(y), adj(beta));
+  STAN_CUDA_PARITY("inv_gamma, the model statement", inv_gamma_lpdf(d.y_pos, alpha0, beta),
+                   inv_gamma_lpdf_reference_cpu<false>(d.y_pos, alpha0, beta), adj(beta));
+  STAN_CUDA_PARITY("inv_gamma propto, var y only", inv_gamma_lpdf<true>(y, al_d, d.sigma),
+                   inv_gamma_lpdf_reference_cpu<true>(y, al_d, d.sigma), adj(y));
+  {  // d/dalpha = -digamma(alpha) + log(beta) - log(y): against the magnitude of its terms
+    var lp = inv_gamma_lpdf(d.y_pos, alpha, beta0);
+    lp.grad();
+    VectorXd g = adj(alpha);
+    set_zero_all_adjoints();
+    var lp_ref = inv_gamma_lpdf_reference_cpu<false>(d.y_pos, alpha, beta0);
+    lp_ref.grad();
+    expect_rel(lp.val(), lp_ref.val(), std::fabs(lp_ref.val()), "inv_gamma, var shape vector: value");
+    for (int i = 0; i < n; ++i) {
+      const double terms = std::fabs(digamma(al_d[i])) + std::fabs(std::log(1.3)) + std::fabs(std::log(d.y_pos[i]));
+      EXPECT_LE(std::fabs(g[i] - alpha[i].adj()), 1e-10 * std::max(std::fabs(alpha[i].adj()), terms)) << "inv_gamma d/dalpha " << i;
+    }
+    set_zero_all_adjoints();
+  }
+  const double v = inv_gamma_lpdf(d.y_pos, al_d, d.sigma);
+  expect_rel(v, inv_gamma_lpdf_reference_cpu<false>(d.y_pos, al_d, d.sigma), std::fabs(v), "inv_gamma, all double");
+  EXPECT_EQ(0.0, inv_gamma_lpdf<true>(d.y_pos, al_d, d.sigma));
+  VectorXd y_zero = d.y_pos;
+  y_zero[0] = 0.0;
+  EXPECT_EQ(LOG_ZERO, inv_gamma_lpdf(y_zero, alpha, beta).val());   // :58-63
+  vector_v alpha_bad = to_v(al_d);
+  alpha_bad[0] = -1.0;
+  EXPECT_THROW(inv_gamma_lpdf(d.y_pos, alpha_bad, beta), std::domain_error);
+  stan::math::recover_memory();
+}
+
 // partials made of terms that may cancel (digamma differences, (1 - p)(log y - log sigma), ...) are compared against the
 // magnitude `floor` of those terms, like student_t's d/dnu (tests/test_locscale.py has the same gates)
 void expect_floor(double got, double ref, double floor, const char* what, int i) {

@@ -109,6 +109,20 @@ for density, yy, aa, ss in (("beta", yb, ab, bb), ("weibull", yw, aw, sw)):
     add(density + "_scalar_y", density, [0.3], aa[:n], ss[:n], var_mask=0b111)
     add(density + "_scalar_second", density, yy[:n], aa[:n], [0.8], var_mask=0b110)
 
+# inv_gamma_lpdf(y | alpha, beta): known answers of test/prob/inv_gamma/inv_gamma_test.hpp:14-25, every subset of variables x
+# propto, scalar / vector operands
+for i, (y, a, b, ka) in enumerate([(1.0, 1.0, 1.0, -1.0), (0.5, 2.9, 3.1, -0.8185294827413338580868)]):
+    add("inv_gamma_ka%d" % i, "inv_gamma", [y], [a], [b], var_mask=0b111, known_answer=ka)
+# (the gamma corners 1e-300 / 1e8 overflow 1 / y^2 in the reference itself: milder ones here)
+yi = np.concatenate([yg[:n], [1e-3, 1e3, 0.5, 3.0]])
+ai = np.concatenate([al[:n], [0.5, 150.0, 1.4616321449683623, 30.0]])
+bi = np.concatenate([be[:n], [1e-3, 1e3, 2.0, 0.05]])
+for var_mask in range(8):
+    for propto in (False, True):
+        add("inv_gamma_vec_m%d%s" % (var_mask, "_propto" if propto else ""), "inv_gamma", yi, ai, bi, propto=propto, var_mask=var_mask)
+add("inv_gamma_scalar_alpha_beta", "inv_gamma", yg[:n], [2.2], [1.3], var_mask=0b111)
+add("inv_gamma_scalar_y", "inv_gamma", [2.5], al[:n], be[:n], var_mask=0b111)
+
 out["cases"] = np.array(names)
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "locscale_golden.npz")
 np.savez_compressed(path, **out)

@@ -80,7 +80,7 @@ def check_case(r, c, what, rtol=1e-10):
     assert r["rc"] == 0, what
     assert_close(r["lp"], c["lp"], what + " lp", rtol)
     for k, bit in KEYS:
-        if c["var_mask"] & bit and k == "dmu" and c.get("density") == _abi.LOCSCALE_GAMMA:
+        if c["var_mask"] & bit and k == "dmu" and c.get("density") in (_abi.LOCSCALE_GAMMA, _abi.LOCSCALE_INV_GAMMA):
             check_gamma_dalpha(r[k], np.asarray(c[k], float), c, what, rtol)
         elif c["var_mask"] & bit and k != "dy" and c.get("density") == _abi.LOCSCALE_BETA:
             check_beta_shape_partial(r[k], np.asarray(c[k], float), c, k, what, rtol)
@@ -101,7 +101,7 @@ def check_case(r, c, what, rtol=1e-10):
 def test_oracle_matches_golden_and_known_answers(golden_ls):
     """outputs of the compiled reference and the literal expected values of test/prob/cauchy/cauchy_test.hpp:10-31,
     test/prob/lognormal/lognormal_test.hpp:10-25"""
-    assert len(golden_ls["cases"]) >= 124
+    assert len(golden_ls["cases"]) >= 144
     known = 0
     for name in golden_ls["cases"]:
         c = ls_case(golden_ls, str(name))
@@ -110,7 +110,7 @@ def test_oracle_matches_golden_and_known_answers(golden_ls):
         if "known_answer" in c:
             known += 1
             assert abs(r["lp"] - c["known_answer"]) <= 1e-13 * max(1.0, abs(c["known_answer"])), name
-    assert known == 16   # 3 cauchy, 2 lognormal, 3 gamma, 3 exponential, 2 beta, 3 weibull
+    assert known == 18   # 3 cauchy, 2 lognormal, 3 gamma, 3 exponential, 2 beta, 3 weibull, 2 inv_gamma
 
 
 def test_oracle_codes():
@@ -139,6 +139,11 @@ def test_oracle_codes():
     for bad_y in (np.inf, np.nan):
         assert L.oracle_locscale_lpdf("weibull", [bad_y], [1.0], [1.0])["rc"] == _abi.BAD_OPERAND
     assert L.oracle_locscale_lpdf("weibull", [1.0, -0.5], [1.0], [1.0])["rc"] == _abi.LOG_ZERO   # weibull_lpdf.hpp:56-61
+    for bad in (0.0, -1.0, np.inf, np.nan):              # test/prob/inv_gamma/inv_gamma_test.hpp:30-55
+        assert L.oracle_locscale_lpdf("inv_gamma", [0.5], [bad], [1.0])["rc"] == _abi.BAD_OPERAND
+        assert L.oracle_locscale_lpdf("inv_gamma", [0.5], [1.0], [bad])["rc"] == _abi.BAD_OPERAND
+    assert L.oracle_locscale_lpdf("inv_gamma", [np.nan], [1.0], [1.0])["rc"] == _abi.BAD_OPERAND
+    assert L.oracle_locscale_lpdf("inv_gamma", [1.0, 0.0], [1.0], [1.0])["rc"] == _abi.LOG_ZERO      # inv_gamma_lpdf.hpp:58-63
     for bad_y in (-10.0, np.nan):                       # test/prob/exponential/exponential_test.hpp:31-36
         assert L.oracle_locscale_lpdf("exponential", [bad_y], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
     assert L.oracle_locscale_lpdf("lognormal", [-1.0], [0.0], [1.0])["rc"] == _abi.BAD_OPERAND
@@ -154,9 +159,9 @@ def synth(density, n, rng):
     mu, sg = rng.standard_normal(n), rng.uniform(0.3, 3.0, n)
     if density == "lognormal":
         y = np.exp(y)
-    elif density in ("gamma", "exponential"):
-        y = rng.gamma(2.0, 1.5, n)
-        mu = rng.uniform(0.2, 8.0, n) if density == "gamma" else np.zeros(1)
+    elif density in ("gamma", "exponential", "inv_gamma"):
+        y = rng.gamma(2.0, 1.5, n) + (1e-3 if density == "inv_gamma" else 0.0)
+        mu = np.zeros(1) if density == "exponential" else rng.uniform(0.2, 8.0, n)
     elif density == "beta":
         y, mu, sg = rng.beta(2.0, 3.0, n).clip(1e-9, 1 - 1e-9), rng.uniform(0.3, 6.0, n), rng.uniform(0.3, 6.0, n)
     elif density == "weibull":
@@ -168,7 +173,7 @@ def masks(density):
     return (0, 1, 4, 5) if density == "exponential" else range(8)
 
 
-DENSITIES = ["normal", "cauchy", "lognormal", "gamma", "exponential", "beta", "weibull"]
+DENSITIES = ["normal", "cauchy", "lognormal", "gamma", "exponential", "beta", "weibull", "inv_gamma"]
 
 
 @needs_ref
@@ -186,7 +191,7 @@ def test_oracle_vs_compiled_reference(density):
                 assert_close(got["lp"], ref["lp"], "%s lp" % density, 1e-12)
                 c = {"y": ops[0], "mu": ops[1], "sigma": ops[2]}
                 for k, bit in KEYS:
-                    if var_mask & bit and k == "dmu" and density == "gamma":
+                    if var_mask & bit and k == "dmu" and density in ("gamma", "inv_gamma"):
                         check_gamma_dalpha(got[k], ref[k], c, "gamma", 1e-12)
                     elif var_mask & bit and k != "dy" and density == "beta":
                         check_beta_shape_partial(got[k], ref[k], c, k, "beta", 1e-12)
@@ -342,12 +347,13 @@ def test_device_beta_and_weibull_wrappers(glm, golden_ls):
     (beta_lpdf.hpp:48-56, weibull_lpdf.hpp:38-61; the invalid values of the reference's fixtures)"""
     for name in golden_ls["cases"]:
         c = ls_case(golden_ls, str(name))
-        f = {_abi.LOCSCALE_BETA: glm.beta_lpdf, _abi.LOCSCALE_WEIBULL: glm.weibull_lpdf}.get(c["density"])
+        f = {_abi.LOCSCALE_BETA: glm.beta_lpdf, _abi.LOCSCALE_WEIBULL: glm.weibull_lpdf,
+             _abi.LOCSCALE_INV_GAMMA: glm.inv_gamma_lpdf}.get(c["density"])
         if f is None:
             continue
         lp, g = f(c["y"], c["mu"], c["sigma"], propto=c["propto"], var_mask=c["var_mask"])
         assert_close(lp, c["lp"], "wrapper vs golden %s lp" % name)
-        assert sorted(g) == sorted(nm for nm, bit in (("y", 1), ("alpha", 2), ("beta" if f is glm.beta_lpdf else "sigma", 4))
+        assert sorted(g) == sorted(nm for nm, bit in (("y", 1), ("alpha", 2), ("sigma" if f is glm.weibull_lpdf else "beta", 4))
                                    if c["var_mask"] & bit)
     n = 3000
     y, a, b = np.linspace(0.05, 0.95, n), np.linspace(0.5, 4, n), np.linspace(0.5, 2, n)
@@ -376,3 +382,9 @@ def test_device_beta_and_weibull_wrappers(glm, golden_ls):
     yy[9] = np.inf
     with pytest.raises(glm.DomainError):
         glm.weibull_lpdf(yy, a, b)
+    yy[9] = 0.0
+    lp, g = glm.inv_gamma_lpdf(yy, a, b)        # an outcome that is not positive: LOG_ZERO
+    assert lp == -np.inf and g == {}
+    yy[9] = np.nan
+    with pytest.raises(glm.DomainError):
+        glm.inv_gamma_lpdf(yy, a, b)

@@ -244,11 +244,32 @@ def test_reference_error_contract():
 @needs_ref
 def test_reference_map_rect_baseline_matches_plain_call():
     """The TBB map_rect row-sharded baseline computes the same value and gradient as one call."""
-    s = synth_glm("poisson_log", 4000, 16, seed=5)
-    plain = L.ref_glm("poisson_log", s["x"], s["y"], s["alpha"], s["beta"])
-    sh = L.RefShards("poisson_log", s["x"], s["y"], n_shards=8, n_threads=4)
-    r = sh.eval(s["beta"], alpha=s["alpha"])
-    sh.close()
-    assert_close(r["lp"], plain["lp"], "map_rect lp", 1e-12)
-    assert_close(r["dbeta"], plain["dbeta"], "map_rect dbeta", 1e-11)
-    assert_close(r["dalpha"], plain["dalpha"], "map_rect dalpha", 1e-11)
+    # In a process of its own: the baseline starts the reference's TBB scheduler, whose worker threads and the library
+    # that holds their code are torn down in no particular order when an interpreter exits (the crash at exit that
+    # bench.py --impl reference avoids the same way) -- the test session must not inherit that.
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import json, os, sys\n"
+        "sys.path.insert(0, %r)\n"
+        "from oracle import loader as L\n"
+        "from tests.helpers import synth_glm\n"
+        "s = synth_glm('poisson_log', 4000, 16, seed=5)\n"
+        "plain = L.ref_glm('poisson_log', s['x'], s['y'], s['alpha'], s['beta'])\n"
+        "sh = L.RefShards('poisson_log', s['x'], s['y'], n_shards=8, n_threads=4)\n"
+        "r = sh.eval(s['beta'], alpha=s['alpha'])\n"
+        "sh.close()\n"
+        "out = {k: [float(v) for v in __import__('numpy').atleast_1d(d[k])] for d, k in ((r, 'lp'), (r, 'dbeta'), (r, 'dalpha'))}\n"
+        "ref = {k: [float(v) for v in __import__('numpy').atleast_1d(plain[k])] for k in ('lp', 'dbeta', 'dalpha')}\n"
+        "print(json.dumps({'got': out, 'ref': ref}))\n"
+        "sys.stdout.flush()\n"
+        "os._exit(0)\n" % root)
+    run = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root, timeout=600)
+    assert run.returncode == 0, run.stderr[-2000:]
+    res = json.loads(run.stdout.strip().splitlines()[-1])
+    assert_close(res["got"]["lp"], res["ref"]["lp"], "map_rect lp", 1e-12)
+    assert_close(res["got"]["dbeta"], res["ref"]["dbeta"], "map_rect dbeta", 1e-11)
+    assert_close(res["got"]["dalpha"], res["ref"]["dalpha"], "map_rect dalpha", 1e-11)
