@@ -31,7 +31,7 @@ BINARIES = ["cuda_glm_parity_test", "ref_bernoulli_logit_glm_lpmf_test", "ref_po
             "cuda_locscale_distr_test", "cuda_locscale_parity_test", "ref_cauchy_test", "ref_lognormal_test",
             "ref_cauchy_log_test", "ref_lognormal_log_test", "ref_gamma_test", "ref_exponential_test", "ref_gamma_log_test",
             "ref_exponential_log_test", "ref_beta_test", "ref_weibull_test", "ref_beta_log_test", "ref_weibull_log_test",
-            "ref_inv_gamma_test", "ref_inv_gamma_log_test"]
+            "ref_inv_gamma_test", "ref_inv_gamma_log_test", "ref_mix_normal_test", "ref_rev_normal_log_test", "ref_fwd_normal_test"]
 
 
 @pytest.mark.gpu
