@@ -12,6 +12,12 @@
  *       whose expected values are stored in tests/golden/ as produced by the reference itself
  *       (oracle/_ref/libstanref.so, generator tests/golden/make_golden.py),
  *   (c) the compiled reference on random inputs whenever oracle/_ref/libstanref.so is present.
+ *   (d) round 2: the reference-generated vectors of the widened rows -- tests/golden/student_t_golden.npz,
+ *       density2_golden.npz (poisson_lpmf, bernoulli_lpmf), locscale_golden.npz (cauchy, lognormal, gamma, exponential,
+ *       beta, weibull, inv_gamma), dense_golden.npz (multiply, cholesky_decompose and its reverse sweep, mdivide_left_tri,
+ *       gp_exp_quad_cov) -- each with the literal known answers of the reference's own test fixtures (test/prob/...)
+ *       stored beside the reference's outputs, generators committed next to them (tests/golden/make_*_golden.py);
+ *       tests/test_oracle.py, test_student_t.py, test_locscale.py and test_dense.py run the comparisons.
  *
  * It takes the same argument structs as the product's C ABI (include/stan_cuda.h) so a test can
  * hand identical arguments to both.  Sums run sequentially in double, in row order; the
